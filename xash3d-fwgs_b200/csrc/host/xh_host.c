@@ -1,0 +1,542 @@
+/*
+ * xh_host.c - headless engine stand-in: ref_api_t callbacks + renderer loader.
+ *
+ * Plays the role of engine/client/dll_int/ref_common.c (R_LoadProgs :547,
+ * R_Init :742, R_CreateBuiltinTextures :494) and the handful of engine
+ * services a renderer consumes.  It is written from the
+ * ABI in engine/ref_api.h; it is not a copy of engine code.
+ */
+#define _GNU_SOURCE
+#include <dlfcn.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "xh_internal.h"
+#include "pm_defs.h"
+
+xh_state_t xh;
+
+/* ------------------------------------------------------------------ */
+/* errors / console                                                     */
+
+static char xh_errbuf[1024];
+
+const char *xh_last_error( void ) { return xh_errbuf; }
+
+static void xh_Con_Printf( const char *fmt, ... )
+{
+	xh.callbacks++;
+	if( !xh.verbose ) return;
+	va_list ap; va_start( ap, fmt ); vfprintf( stderr, fmt, ap ); va_end( ap );
+}
+
+static void xh_Con_Quiet( const char *fmt, ... ) { xh.callbacks++; (void)fmt; }
+
+static void xh_Host_Error( const char *fmt, ... )
+{
+	va_list ap; va_start( ap, fmt ); vsnprintf( xh_errbuf, sizeof( xh_errbuf ), fmt, ap ); va_end( ap );
+	fprintf( stderr, "[xh_host] Host_Error: %s\n", xh_errbuf );
+	/* the engine longjmps to the console here; a test harness has no console to go to */
+	abort();
+}
+
+/* ------------------------------------------------------------------ */
+/* memory pools: plain malloc with a size header (for realloc-with-clear) */
+
+typedef struct { size_t size; size_t pad; } xh_memhdr_t;
+
+static poolhandle_t xh_Mem_AllocPool( const char *name, unsigned int flags, const char *file, int line )
+{
+	(void)name; (void)flags; (void)file; (void)line;
+	return ++xh.npools;
+}
+
+static void xh_Mem_FreePool( poolhandle_t *pool, const char *file, int line )
+{
+	(void)file; (void)line;
+	if( pool ) *pool = 0; /* allocations are leaked on purpose: process-lifetime harness */
+}
+
+static void *xh_Mem_Alloc( poolhandle_t pool, size_t size, qboolean clear, const char *file, int line )
+{
+	(void)pool; (void)file; (void)line;
+	xh_memhdr_t *h = clear ? calloc( 1, sizeof( *h ) + size + 64 ) : malloc( sizeof( *h ) + size + 64 );
+	if( !h ) xh_Host_Error( "out of memory (%zu bytes)", size );
+	h->size = size;
+	return h + 1;
+}
+
+static void xh_Mem_Free( void *data, const char *file, int line )
+{
+	(void)file; (void)line;
+	if( data ) free((xh_memhdr_t *)data - 1 );
+}
+
+static void *xh_Mem_Realloc( poolhandle_t pool, void *ptr, size_t size, qboolean clear, const char *file, int line )
+{
+	if( !ptr ) return xh_Mem_Alloc( pool, size, clear, file, line );
+	xh_memhdr_t *h = (xh_memhdr_t *)ptr - 1;
+	size_t old = h->size;
+	h = realloc( h, sizeof( *h ) + size + 64 );
+	if( !h ) xh_Host_Error( "out of memory (%zu bytes)", size );
+	if( clear && size > old ) memset((byte *)( h + 1 ) + old, 0, size - old );
+	h->size = size;
+	return h + 1;
+}
+
+void *xh_alloc( size_t size ) { return xh_Mem_Alloc( 0, size, true, __FILE__, __LINE__ ); }
+
+/* ------------------------------------------------------------------ */
+/* cvars: linked list of convar_t (common/cvardef.h:97)                 */
+
+static convar_t *xh_cvar_find( const char *name )
+{
+	for( convar_t *c = xh.cvars; c; c = c->next )
+		if( !strcasecmp( c->name, name )) return c;
+	return NULL;
+}
+
+static void xh_cvar_assign( convar_t *c, const char *value )
+{
+	c->string = strdup( value );
+	c->value = (float)atof( value );
+	c->flags |= FCVAR_CHANGED;
+}
+
+static convar_t *xh_cvar_create( const char *name, const char *value, int flags )
+{
+	convar_t *c = xh_cvar_find( name );
+	if( c ) return c;
+	c = calloc( 1, sizeof( *c ));
+	c->name = strdup( name );
+	c->desc = (char *)"";
+	c->def_string = strdup( value );
+	c->flags = flags | FCVAR_ALLOCATED;
+	xh_cvar_assign( c, value );
+	c->flags &= ~FCVAR_CHANGED;
+	c->next = xh.cvars; xh.cvars = c;
+	return c;
+}
+
+/* a renderer-owned static convar_t (CVAR_DEFINE) being linked in (engine/common/cvar.c Cvar_RegisterVariable) */
+static void xh_Cvar_RegisterVariable( convar_t *var )
+{
+	xh.callbacks++;
+	convar_t *old = xh_cvar_find( var->name );
+	const char *value = var->string;
+	char *preset = NULL;
+	if( old )
+	{
+		/* value preset by the harness before the renderer registered its own variable: keep it, unlink ours */
+		preset = strdup( old->string );
+		value = preset;
+		for( convar_t **pp = &xh.cvars; *pp; pp = &( *pp )->next )
+			if( *pp == old ) { *pp = old->next; break; }
+	}
+	var->def_string = var->string;
+	var->string = strdup( value );
+	var->value = (float)atof( value );
+	var->next = xh.cvars; xh.cvars = var;
+	free( preset );
+}
+
+static cvar_t *xh_Cvar_Get( const char *name, const char *value, int flags, const char *desc )
+{
+	(void)desc; xh.callbacks++;
+	return (cvar_t *)xh_cvar_create( name, value, flags );
+}
+
+static cvar_t *xh_GetCvarPointer( const char *name ) { xh.callbacks++; return (cvar_t *)xh_cvar_find( name ); }
+static float xh_GetCvarFloat( const char *name ) { convar_t *c = xh_cvar_find( name ); return c ? c->value : 0.0f; }
+static const char *xh_GetCvarString( const char *name ) { convar_t *c = xh_cvar_find( name ); return c ? c->string : ""; }
+static void xh_Cvar_Set( const char *name, const char *value )
+{
+	convar_t *c = xh_cvar_find( name );
+	if( !c ) c = xh_cvar_create( name, value, 0 );
+	xh_cvar_assign( c, value );
+}
+static void xh_Cvar_SetValue( const char *name, float value )
+{
+	char buf[64]; snprintf( buf, sizeof( buf ), "%g", value ); xh_Cvar_Set( name, buf );
+}
+static void xh_Cvar_FullSet( const char *name, const char *value, int flags ) { (void)flags; xh_Cvar_Set( name, value ); }
+
+void xh_cvar_set( const char *name, const char *value ) { xh_Cvar_Set( name, value ); }
+float xh_cvar_get( const char *name ) { return xh_GetCvarFloat( name ); }
+
+/* ------------------------------------------------------------------ */
+/* small engine services                                                */
+
+static int xh_Cmd_AddCommand( const char *n, void (*f)( void ), const char *d ) { (void)n; (void)f; (void)d; return 1; }
+static void xh_Cmd_RemoveCommand( const char *n ) { (void)n; }
+static int xh_Cmd_Argc( void ) { return 0; }
+static const char *xh_Cmd_Argv( int i ) { (void)i; return ""; }
+static const char *xh_Cmd_Args( void ) { return ""; }
+static void xh_Cbuf_Text( const char *t ) { (void)t; }
+static void xh_Cbuf_Execute( void ) {}
+static void xh_void( void ) { xh.callbacks++; }
+static int xh_Sys_CheckParm( const char *flag ) { (void)flag; return 0; }
+static qboolean xh_R_Init_Video( ref_graphic_apis_t type ) { return type == REF_SOFTWARE; }
+
+/* deterministic LCG in place of engine/common/common.c COM_RandomLong: the value only feeds
+ * rtable[][] (random tiling textures "-0name"), identical for every renderer under this host */
+static void xh_SetRandomSeed( int seed ) { xh.rng = (uint32_t)seed; }
+static int xh_RandomLong( int lo, int hi )
+{
+	xh.rng = xh.rng * 1664525u + 1013904223u;
+	uint32_t span = (uint32_t)( hi - lo + 1 );
+	return span ? lo + (int)(( xh.rng >> 8 ) % span ) : lo;
+}
+static float xh_RandomFloat( float lo, float hi )
+{
+	xh.rng = xh.rng * 1664525u + 1013904223u;
+	return lo + ( hi - lo ) * (float)(( xh.rng >> 8 ) & 0xFFFF ) / 65535.0f;
+}
+
+static intptr_t xh_EngineGetParm( int parm, int arg )
+{
+	(void)arg; xh.callbacks++;
+	switch( parm )
+	{
+	case PARM_GET_CLIENT_PTR: return (intptr_t)&xh.cl;
+	case PARM_GET_HOST_PTR: return (intptr_t)&xh.host;
+	case PARM_GET_MOVEVARS_PTR: return (intptr_t)&xh.movevars;
+	case PARM_GET_PALETTE_PTR: return (intptr_t)xh.palette;
+	case PARM_GET_VIEWENT_PTR: return (intptr_t)&xh.viewent;
+	case PARM_GET_TEXGAMMATABLE_PTR: return (intptr_t)xh.texgamma;
+	case PARM_GET_LIGHTGAMMATABLE_PTR: return (intptr_t)xh.lightgamma;
+	case PARM_GET_SCREENGAMMATABLE_PTR: return (intptr_t)xh.screengamma;
+	case PARM_GET_LINEARGAMMATABLE_PTR: return (intptr_t)xh.lineargamma;
+	case PARM_GET_LIGHTSTYLES_PTR: return (intptr_t)xh.lightstyles;
+	case PARM_GET_DLIGHTS_PTR: return (intptr_t)xh.dlights;
+	case PARM_GET_ELIGHTS_PTR: return (intptr_t)xh.elights;
+	case PARM_GET_WORLD_PTR: return 0;
+	case PARM_CONNSTATE: return 5; /* ca_active, engine/client/client.h */
+	case PARM_SINGLEPLAYER_GAME: return 1;
+	case PARM_NUMENTITIES: return xh.num_entities;
+	case PARM_THIRDPERSON: case PARM_DEV_OVERVIEW: case PARM_QUAKE_COMPATIBLE:
+	case PARM_PLAYING_DEMO: case PARM_WATER_LEVEL: return 0;
+	case PARM_LOCAL_HEALTH: return 100;
+	default: return 0;
+	}
+}
+
+/* software "window": the engine hands out an RGB565 surface (engine/platform/sdl2/vid_sdl2.c:52-229) */
+static qboolean xh_SW_CreateBuffer( int w, int h, uint *stride, uint *bpp, uint *r, uint *g, uint *b )
+{
+	free( xh.swbuffer );
+	xh.swbuffer = calloc((size_t)w * h, 2 );
+	xh.sw_w = w; xh.sw_h = h;
+	*stride = w; *bpp = 2; *r = 0xF800; *g = 0x07E0; *b = 0x001F;
+	return xh.swbuffer != NULL;
+}
+static void *xh_SW_LockBuffer( void ) { return xh.swbuffer; }
+static void xh_SW_UnlockBuffer( void ) {}
+
+static void xh_R_StoreEfrags( struct efrag_s **pp, int framecount ) { (void)pp; (void)framecount; }
+static void xh_CL_DrawEFX( float time, qboolean trans ) { (void)time; (void)trans; xh.callbacks++; }
+static struct cl_entity_s *xh_R_BeamGetEntity( int i ) { (void)i; return NULL; }
+static void *xh_Mod_Extradata( int type, model_t *m ) { (void)type; return m ? m->cache.data : NULL; }
+static int xh_GL_SetAttribute( int a, int v ) { (void)a; (void)v; return 0; }
+static int xh_GL_GetAttribute( int a, int *v ) { (void)a; if( v ) *v = 0; return 0; }
+static void *xh_GL_GetProcAddress( const char *n ) { (void)n; return NULL; }
+static double xh_Time( void ) { return xh.host.realtime; }
+static void xh_Image_SetForceFlags( uint f ) { (void)f; }
+static void xh_Image_ClearForceFlags( void ) {}
+static qboolean xh_Image_CustomPalette( void ) { return false; }
+static void xh_Image_SetMDLPointer( byte *p ) { (void)p; }
+static qboolean xh_Image_Process( rgbdata_t **pix, int w, int h, uint flags, float r ) { (void)pix; (void)w; (void)h; (void)flags; (void)r; return true; }
+
+/* world as physent 0 (pmove->physents[0], engine/client/cl_pmove.c): light tracing walks it */
+static struct physent_s *xh_EV_GetPhysent( int idx )
+{
+	static physent_t world;
+	if( idx != 0 || !xh.world ) return NULL;
+	memset( &world, 0, sizeof( world ));
+	strcpy( world.name, "world" );
+	world.model = xh.world;
+	world.solid = SOLID_BSP;
+	return &world;
+}
+static void xh_SetLocalLightLevel( int level ) { (void)level; }
+static void *xh_null_ptr( void ) { return NULL; }
+
+/* ------------------------------------------------------------------ */
+/* trap stubs for every slot we do not implement: a call is a harness bug, say which */
+
+#define XH_NSTUBS 128
+static void xh_trap( int idx )
+{
+	fprintf( stderr, "[xh_host] renderer called unimplemented ref_api_t slot #%d (see engine/ref_api.h:368-520)\n", idx );
+	abort();
+}
+#define S1( n ) static intptr_t xh_stub_##n( void ) { xh_trap( n ); return 0; }
+#define S10( d ) S1( d##0 ) S1( d##1 ) S1( d##2 ) S1( d##3 ) S1( d##4 ) S1( d##5 ) S1( d##6 ) S1( d##7 ) S1( d##8 ) S1( d##9 )
+S1( 0 ) S1( 1 ) S1( 2 ) S1( 3 ) S1( 4 ) S1( 5 ) S1( 6 ) S1( 7 ) S1( 8 ) S1( 9 )
+S10( 1 ) S10( 2 ) S10( 3 ) S10( 4 ) S10( 5 ) S10( 6 ) S10( 7 ) S10( 8 ) S10( 9 ) S10( 10 ) S10( 11 )
+S1( 120 ) S1( 121 ) S1( 122 ) S1( 123 ) S1( 124 ) S1( 125 ) S1( 126 ) S1( 127 )
+#undef S1
+#define S1( n ) xh_stub_##n,
+static intptr_t (*const xh_stubs[XH_NSTUBS])( void ) = {
+	S1( 0 ) S1( 1 ) S1( 2 ) S1( 3 ) S1( 4 ) S1( 5 ) S1( 6 ) S1( 7 ) S1( 8 ) S1( 9 )
+	S10( 1 ) S10( 2 ) S10( 3 ) S10( 4 ) S10( 5 ) S10( 6 ) S10( 7 ) S10( 8 ) S10( 9 ) S10( 10 ) S10( 11 )
+	S1( 120 ) S1( 121 ) S1( 122 ) S1( 123 ) S1( 124 ) S1( 125 ) S1( 126 ) S1( 127 )
+};
+
+static void xh_fill_engfuncs( ref_api_t *e )
+{
+	/* every slot is a pointer: point all of them at numbered traps first */
+	void **slots = (void **)e;
+	size_t n = sizeof( *e ) / sizeof( void * );
+	for( size_t i = 0; i < n; i++ )
+		slots[i] = (void *)xh_stubs[i < XH_NSTUBS ? i : XH_NSTUBS - 1];
+
+	e->EngineGetParm = xh_EngineGetParm;
+	e->Cvar_Get = xh_Cvar_Get;
+	e->pfnGetCvarPointer = xh_GetCvarPointer;
+	e->pfnGetCvarFloat = xh_GetCvarFloat;
+	e->pfnGetCvarString = xh_GetCvarString;
+	e->Cvar_SetValue = xh_Cvar_SetValue;
+	e->Cvar_Set = xh_Cvar_Set;
+	e->Cvar_RegisterVariable = xh_Cvar_RegisterVariable;
+	e->Cvar_FullSet = xh_Cvar_FullSet;
+	e->Cmd_AddCommand = xh_Cmd_AddCommand;
+	e->Cmd_RemoveCommand = xh_Cmd_RemoveCommand;
+	e->Cmd_Argc = xh_Cmd_Argc;
+	e->Cmd_Argv = xh_Cmd_Argv;
+	e->Cmd_Args = xh_Cmd_Args;
+	e->Cbuf_AddText = xh_Cbuf_Text;
+	e->Cbuf_InsertText = xh_Cbuf_Text;
+	e->Cbuf_Execute = xh_Cbuf_Execute;
+	e->Con_Printf = xh_Con_Printf;
+	e->Con_DPrintf = xh_Con_Quiet;
+	e->Con_Reportf = xh_Con_Quiet;
+	e->R_BeamGetEntity = xh_R_BeamGetEntity;
+	e->Mod_SampleSizeForFace = xh_Mod_SampleSizeForFace;
+	e->Mod_BoxVisible = xh_Mod_BoxVisible;
+	e->Mod_PointInLeaf = xh_Mod_PointInLeaf;
+	e->CL_DrawEFX = xh_CL_DrawEFX;
+	e->R_StoreEfrags = xh_R_StoreEfrags;
+	e->Mod_Extradata = xh_Mod_Extradata;
+	e->CL_ExtraUpdate = xh_void;
+	e->Host_Error = xh_Host_Error;
+	e->COM_SetRandomSeed = xh_SetRandomSeed;
+	e->COM_RandomFloat = xh_RandomFloat;
+	e->COM_RandomLong = xh_RandomLong;
+	e->Sys_CheckParm = xh_Sys_CheckParm;
+	e->_Mem_AllocPool = xh_Mem_AllocPool;
+	e->_Mem_FreePool = xh_Mem_FreePool;
+	e->_Mem_Alloc = xh_Mem_Alloc;
+	e->_Mem_Realloc = xh_Mem_Realloc;
+	e->_Mem_Free = xh_Mem_Free;
+	e->R_Init_Video = xh_R_Init_Video;
+	e->R_Free_Video = xh_void;
+	e->GL_SetAttribute = xh_GL_SetAttribute;
+	e->GL_GetAttribute = xh_GL_GetAttribute;
+	e->GL_GetProcAddress = xh_GL_GetProcAddress;
+	e->GL_SwapBuffers = xh_void;
+	e->SW_CreateBuffer = xh_SW_CreateBuffer;
+	e->SW_LockBuffer = xh_SW_LockBuffer;
+	e->SW_UnlockBuffer = xh_SW_UnlockBuffer;
+	e->R_FatPVS = xh_R_FatPVS;
+	e->pfnTime = xh_Time;
+	e->Image_SetForceFlags = xh_Image_SetForceFlags;
+	e->Image_ClearForceFlags = xh_Image_ClearForceFlags;
+	e->Image_CustomPalette = xh_Image_CustomPalette;
+	e->Image_Process = xh_Image_Process;
+	e->FS_LoadImage = xh_FS_LoadImage;
+	e->FS_CopyImage = xh_FS_CopyImage;
+	e->FS_FreeImage = xh_FS_FreeImage;
+	e->Image_SetMDLPointer = xh_Image_SetMDLPointer;
+	e->EV_GetPhysent = xh_EV_GetPhysent;
+	e->SetLocalLightLevel = xh_SetLocalLightLevel;
+	e->CL_GetRemapInfoForEntity = (void *)xh_null_ptr;
+	e->pfnPlayerInfo = (void *)xh_null_ptr;
+	e->pfnGetPlayerState = (void *)xh_null_ptr;
+	e->GetDefaultSprite = (void *)xh_null_ptr;
+	e->R_GetSpriteFrame = (void *)xh_null_ptr;
+	e->R_StudioGetAnim = (void *)xh_null_ptr;
+	e->CL_AllocElight = (void *)xh_null_ptr;
+	e->EV_TraceSurface = (void *)xh_null_ptr;
+	e->GetScreenFade = (void *)xh_null_ptr;
+	e->pfnDrawNormalTriangles = xh_void;
+	e->pfnDrawTransparentTriangles = xh_void;
+	e->drawFuncs = &xh.drawfuncs; /* non-NULL struct of NULL hooks (cl_render.c) */
+	e->fsapi = NULL;
+}
+
+/* ------------------------------------------------------------------ */
+/* default cvars the engine creates before loading a renderer            */
+/* (engine/client/dll_int/ref_common.c:35-44,755-780; engine/client/gamma.c:29-33; ref_api.h:676-703) */
+
+static void xh_default_cvars( void )
+{
+	static const char *const kv[][2] = {
+		{ "gamma", "2.5" }, { "brightness", "0.0" }, { "lightgamma", "2.5" }, { "texgamma", "2.0" }, { "direct", "0.9" },
+		{ "r_showtextures", "0" }, { "r_speeds", "0" }, { "r_fullbright", "0" }, { "r_norefresh", "0" },
+		{ "r_lightmap", "0" }, { "r_dynamic", "1" }, { "r_drawentities", "1" }, { "r_decals", "4096" },
+		{ "r_showhull", "0" }, { "gl_vsync", "1" }, { "gl_clear", "0" }, { "cl_himodels", "1" },
+		{ "cl_lightstyle_lerping", "0" }, { "tracerred", "0.8" }, { "tracergreen", "0.8" }, { "tracerblue", "0.4" },
+		{ "traceralpha", "0.5" }, { "r_sprite_lerping", "1" }, { "r_sprite_lighting", "1" }, { "r_drawviewmodel", "1" },
+		{ "r_glowshellfreq", "2.2" }, { "host_allow_materials", "0" }, { "r_pvs_radius", "0.1" },
+		{ "r_lighting_modulate", "0.6" }, { "r_adjust_fov", "1" },
+	};
+	for( size_t i = 0; i < sizeof( kv ) / sizeof( kv[0] ); i++ )
+		xh_cvar_create( kv[i][0], kv[i][1], 0 );
+}
+
+/* ------------------------------------------------------------------ */
+/* builtin textures the engine creates right after R_Init (ref_common.c:494-545) */
+
+static uint xh_rgba( uint r, uint g, uint b, uint a ) { return r | g << 8 | b << 16 | a << 24; }
+
+static void xh_builtin_textures( void )
+{
+	uint chk[256], part[64], flat[16];
+	for( int y = 0; y < 16; y++ )
+		for( int x = 0; x < 16; x++ )
+			chk[y * 16 + x] = (( y < 8 ) != ( x < 8 )) ? xh_rgba( 255, 0, 255, 255 ) : xh_rgba( 0, 0, 0, 255 );
+	xh.ref.GL_CreateTexture( REF_DEFAULT_TEXTURE, 16, 16, chk, 0 );
+
+	for( int i = 0; i < 64; i++ ) part[i] = xh_rgba( 255, 255, 255, 0 );
+	for( int y = 1; y < 5; y++ )
+		for( int x = 1; x < 5; x++ )
+			if( !(( x == 1 || x == 4 ) && ( y == 1 || y == 4 )))
+				part[y * 8 + x] = xh_rgba( 255, 255, 255, 255 );
+	xh.ref.GL_CreateTexture( REF_PARTICLE_TEXTURE, 8, 8, part, TF_CLAMP | TF_HAS_ALPHA );
+
+	for( int i = 0; i < 16; i++ ) flat[i] = 0xFFFFFFFFu;
+	xh.ref.GL_CreateTexture( REF_WHITE_TEXTURE, 4, 4, flat, 0 );
+	for( int i = 0; i < 16; i++ ) flat[i] = xh_rgba( 127, 127, 127, 255 );
+	xh.ref.GL_CreateTexture( REF_GRAY_TEXTURE, 4, 4, flat, 0 );
+	for( int i = 0; i < 16; i++ ) flat[i] = xh_rgba( 0, 0, 0, 255 );
+	xh.ref.GL_CreateTexture( REF_BLACK_TEXTURE, 4, 4, flat, 0 );
+}
+
+/* ------------------------------------------------------------------ */
+
+int xh_init( const char *ref_path, int width, int height )
+{
+	if( xh.dll ) { snprintf( xh_errbuf, sizeof( xh_errbuf ), "already initialised" ); return -1; }
+
+	xh.verbose = getenv( "XH_VERBOSE" ) != NULL;
+	xh.dll = dlopen( ref_path, RTLD_NOW | RTLD_LOCAL );
+	if( !xh.dll ) { snprintf( xh_errbuf, sizeof( xh_errbuf ), "dlopen: %s", dlerror()); return -2; }
+
+	REFAPI get = (REFAPI)dlsym( xh.dll, GET_REF_API );
+	if( !get ) { snprintf( xh_errbuf, sizeof( xh_errbuf ), "no GetRefAPI in %s", ref_path ); return -3; }
+
+	xh_default_cvars();
+	xh_build_gamma( xh_cvar_get( "gamma" ), xh_cvar_get( "brightness" ), xh_cvar_get( "texgamma" ), xh_cvar_get( "lightgamma" ));
+
+	memset( &xh.refState, 0, sizeof( xh.refState ));
+	xh.refState.width = width; xh.refState.height = height;
+	xh.refState.scale_x = xh.refState.scale_y = 1.0f;
+	xh.refState.desktopBitsPixel = 16;
+	xh.cl.maxclients = 1; xh.cl.playernum = 0; xh.cl.viewentity = 1;
+	xh.cl.time = 1.0; xh.cl.oldtime = 1.0 - 1.0 / 60.0;
+	xh.host.realtime = 1.0; xh.host.frametime = 1.0 / 60.0;
+	xh.movevars.zmax = 4096.0f;
+	for( int i = 0; i < 256; i++ )
+		xh.palette[i].r = xh.palette[i].g = xh.palette[i].b = (byte)i;
+	xh.max_entities = XH_MAX_ENTITIES;
+	xh.entities = calloc( xh.max_entities, sizeof( cl_entity_t ));
+	xh.rng = 0xB200;
+
+	ref_api_t eng;
+	xh_fill_engfuncs( &eng ); /* the engine passes a private copy (ref_common.c:549,571) */
+	if( get( REF_API_VERSION, &xh.ref, &eng, &xh.refState ) != REF_API_VERSION )
+	{
+		snprintf( xh_errbuf, sizeof( xh_errbuf ), "GetRefAPI version mismatch" );
+		return -4;
+	}
+	if( !xh.ref.R_Init())
+	{
+		snprintf( xh_errbuf, sizeof( xh_errbuf ), "R_Init failed" );
+		return -5;
+	}
+	xh_builtin_textures();
+	xh.ref.R_ProcessEntData( true, xh.entities, xh.max_entities );
+	return 0;
+}
+
+void xh_shutdown( void )
+{
+	if( !xh.dll ) return;
+	xh.ref.R_Shutdown();
+	/* the library is left mapped: renderer globals die with the process */
+	xh.dll = NULL;
+}
+
+void *xh_ref_symbol( const char *name ) { return xh.dll ? dlsym( xh.dll, name ) : NULL; }
+uint64_t xh_callback_count( void ) { return xh.callbacks; }
+
+/* ------------------------------------------------------------------ */
+/* time / light styles                                                   */
+
+void xh_set_time( double time, double oldtime )
+{
+	xh.cl.time = time; xh.cl.oldtime = oldtime;
+	xh.host.realtime = time; xh.host.frametime = time - oldtime;
+}
+
+/* engine/client/cl_tent.c:2390-2424 CL_SetLightstyle */
+void xh_set_lightstyle( int style, const char *pattern, float time )
+{
+	if( style < 0 || style >= MAX_LIGHTSTYLES ) return;
+	lightstyle_t *ls = &xh.lightstyles[style];
+	memset( ls, 0, sizeof( *ls ));
+	strncpy( ls->pattern, pattern, sizeof( ls->pattern ) - 1 );
+	ls->length = (int)strlen( ls->pattern );
+	ls->time = time;
+	for( int i = 0; i < ls->length; i++ ) ls->map[i] = (float)( ls->pattern[i] - 'a' );
+	ls->interp = ls->length > 1;
+	for( int i = 0; i < ls->length - 1; i++ )
+		if( fabsf( ls->map[i] - ls->map[( i + 1 ) % ls->length] ) > 3.0f ) { ls->interp = false; break; }
+}
+
+void xh_run_lightstyles( void ) { xh.ref.CL_RunLightStyles( xh.lightstyles ); }
+
+/* ------------------------------------------------------------------ */
+/* frames                                                                */
+
+void xh_begin_frame( void ) { xh.ref.R_BeginFrame( false ); }
+void xh_end_frame( void ) { xh.ref.R_EndFrame(); }
+
+void xh_render_view( const float *origin, const float *angles, float fov_x, float fov_y, int x, int y, int w, int h, int flags )
+{
+	ref_viewpass_t rvp;
+	memset( &rvp, 0, sizeof( rvp ));
+	rvp.viewport[0] = x; rvp.viewport[1] = y; rvp.viewport[2] = w; rvp.viewport[3] = h;
+	for( int i = 0; i < 3; i++ ) { rvp.vieworigin[i] = origin[i]; rvp.viewangles[i] = angles[i]; }
+	rvp.viewentity = xh.cl.viewentity;
+	rvp.fov_x = fov_x; rvp.fov_y = fov_y;
+	rvp.flags = flags;
+	for( int i = 0; i < 3; i++ ) { xh.refState.vieworg[i] = origin[i]; xh.refState.viewangles[i] = angles[i]; }
+	xh.ref.GL_RenderFrame( &rvp );
+}
+
+void xh_clear_scene( void ) { xh.ref.R_ClearScene(); }
+
+int xh_add_brush_entity( int modelindex, const float *origin, const float *angles, int rendermode, int renderamt )
+{
+	if( modelindex <= 1 || modelindex > xh.cl.nummodels || !xh.cl.models[modelindex] ) return -1;
+	if( xh.num_entities >= (int)xh.max_entities ) return -1;
+	int idx = xh.num_entities++;
+	cl_entity_t *e = &xh.entities[idx];
+	memset( e, 0, sizeof( *e ));
+	e->index = idx;
+	e->model = xh.cl.models[modelindex];
+	e->curstate.modelindex = modelindex;
+	e->curstate.rendermode = rendermode;
+	e->curstate.renderamt = renderamt;
+	for( int i = 0; i < 3; i++ )
+	{
+		e->origin[i] = e->curstate.origin[i] = origin[i];
+		e->angles[i] = e->curstate.angles[i] = angles[i];
+	}
+	return xh.ref.R_AddEntity( e, ET_NORMAL ) ? idx : -1;
+}

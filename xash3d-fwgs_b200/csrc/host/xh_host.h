@@ -1,0 +1,72 @@
+/*
+ * xh_host.h - headless engine stand-in ("host") for Xash3D FWGS renderer plugins.
+ *
+ * The real engine (engine/client/dll_int/ref_common.c:547-600) dlopen()s
+ * libref_<name>.so, resolves GetRefAPI and hands it a ref_api_t of engine
+ * callbacks.  The engine client cannot be built on this box (no SDL, missing
+ * submodules), so this small C library plays the engine's part for any
+ * renderer .so: the reference's own ref_soft (the parity oracle / CPU
+ * baseline) and our ref_cuda.  It owns the model_t, the entity list, cvars,
+ * gamma tables and light styles, exactly the things engine/ owns upstream.
+ *
+ * All exported functions are plain C (ctypes-friendly); state is per loaded
+ * copy of this library (the renderer ABI has no context pointer, so one
+ * library image == one engine instance; load a second copy for a second
+ * renderer in the same process).
+ */
+#ifndef XH_HOST_H
+#define XH_HOST_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define XH_EXPORT __attribute__((visibility("default")))
+
+/* dlopen renderer, GetRefAPI handshake, R_Init, builtin textures. 0 on success. */
+XH_EXPORT int xh_init( const char *ref_path, int width, int height );
+XH_EXPORT void xh_shutdown( void );
+
+/* cvars: must be set before xh_init for registration-time values, any time otherwise */
+XH_EXPORT void xh_cvar_set( const char *name, const char *value );
+XH_EXPORT float xh_cvar_get( const char *name );
+
+/* load a BSP30 image from memory as the world (models[1]) + its inline submodels; calls R_NewMap */
+XH_EXPORT int xh_load_map( const void *bsp, size_t len, const char *name );
+
+/* time + light styles (engine/client/cl_tent.c:2390 CL_SetLightstyle, cl_frame.c:1300) */
+XH_EXPORT void xh_set_time( double time, double oldtime );
+XH_EXPORT void xh_set_lightstyle( int style, const char *pattern, float time );
+XH_EXPORT void xh_run_lightstyles( void );
+
+/* one view through ref.GL_RenderFrame (ref_viewpass_t, common/ref_params.h:97) */
+XH_EXPORT void xh_begin_frame( void );
+XH_EXPORT void xh_render_view( const float *origin, const float *angles, float fov_x, float fov_y,
+	int x, int y, int w, int h, int flags );
+XH_EXPORT void xh_end_frame( void );
+
+/* entity list for the next views: R_ClearScene + R_AddEntity */
+XH_EXPORT void xh_clear_scene( void );
+XH_EXPORT int xh_add_brush_entity( int modelindex, const float *origin, const float *angles,
+	int rendermode, int renderamt );
+
+/* raw access for harnesses */
+XH_EXPORT void *xh_ref_symbol( const char *name );      /* dlsym on the renderer .so */
+XH_EXPORT void *xh_world_model( void );                  /* model_t* */
+XH_EXPORT int xh_world_info( int *out, int n );          /* numsurfaces,numnodes,numleafs,numedges,numvertexes,... */
+XH_EXPORT int xh_point_in_leaf( const float *p, int *contents, int *cluster );
+XH_EXPORT int xh_surface_info( int surf, int *out, int n ); /* flags,extents,lightextents,styles,texnum,... */
+XH_EXPORT const void *xh_gamma_table( int which, int *count ); /* 0 tex(u8) 1 light 2 linear 3 screen (u16) */
+XH_EXPORT void xh_build_gamma( float gamma, float brightness, float texgamma, float lightgamma );
+XH_EXPORT uint64_t xh_callback_count( void );            /* engine callbacks hit since init (debug) */
+XH_EXPORT const char *xh_last_error( void );
+/* oracle-only probe: CACHESPOT(surf)[mip] of ref_soft -> surface cache block (r_local.h:781-793,968) */
+XH_EXPORT const void *xh_soft_cache_block( int surf, int mip, int *width, int *height );
+
+#ifdef __cplusplus
+}
+#endif
+#endif
