@@ -1,0 +1,57 @@
+/*
+ * ref_cuda.h - C ABI of libref_cuda.so, the B200-native renderer plugin for Xash3D FWGS.
+ *
+ * 1. The drop-in boundary is the reference's own plugin entry point: the engine dlopen()s
+ *    "libref_cuda.so" for `-ref cuda` (engine/client/dll_int/ref_common.c:547-600), resolves
+ *    GetRefAPI (engine/ref_api.h:660-661) and talks to the renderer only through the ref_interface_t
+ *    table it fills (engine/ref_api.h:527-658).  Replaces ref/common/ref_context.c:57-81 +
+ *    ref/soft/r_context.c:430-533.
+ *
+ * 2. Batch extension (additive; the engine never needs it): the stock ABI renders one view per
+ *    GL_RenderFrame into one screen buffer.  Harnesses that want N independent observations per launch
+ *    (RL-style rendering) resolve the RefCuda_* symbols with dlsym / COM_GetProcAddress.  Plain
+ *    pointers and sizes only.
+ */
+#ifndef REF_CUDA_H
+#define REF_CUDA_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+struct ref_interface_s;
+struct ref_api_s;
+struct ref_globals_s;
+struct ref_viewpass_s;
+
+#define REF_CUDA_EXPORT __attribute__(( visibility( "default" )))
+
+/* engine/ref_api.h:660 REFAPI.  Returns REF_API_VERSION (18) on success, 0 on version mismatch. */
+REF_CUDA_EXPORT int GetRefAPI( int version, struct ref_interface_s *pFunctionTable, struct ref_api_s *engfuncs, struct ref_globals_s *pGlobals );
+
+/*
+ * Render nviews views (common/ref_params.h:97 ref_viewpass_t, the struct GL_RenderFrame takes) of the
+ * current world in one batch.  Every view gets its own screen-sized (ref_globals_t width x height)
+ * buffer: color_out[nviews][height][width] holds ref_soft pixel_t codes (ref/soft/r_local.h:84), z_out the
+ * 16-bit 1/z buffer (d_pzbuffer); either may be NULL to leave the result in HBM.  clear != 0 starts from
+ * zeroed buffers (ref_soft never clears: r_edge.c:983 D_SolidSurf skips the background surface).
+ * Returns 0 on success; errors are also reported through the engine's Host_Error.
+ */
+REF_CUDA_EXPORT int RefCuda_RenderViews( const struct ref_viewpass_s *views, int nviews, unsigned short *color_out, short *z_out, int clear );
+
+/* Re-run the device stages of the last batch with all inputs resident in HBM; CUDA-event milliseconds
+ * per iteration: total and per stage [visibility+BSP walk, face/edge set-up, surface cache, scanlines]. */
+REF_CUDA_EXPORT int RefCuda_BenchResident( int iters, int rebuild_cache, float *ms_total, float *ms_stage );
+
+/* Surface cache block of (surface, mip) as built on the device (D_CacheSurface, ref/soft/r_surf.c:1053). */
+REF_CUDA_EXPORT int RefCuda_ReadSurfaceCache( int surf, int mip, unsigned short *out, int maxtexels, int *width, int *height, int *valid );
+
+/* Counters of the last batch (rc_shared.h RC_CTR_*), kernels launched since R_Init, device name. */
+REF_CUDA_EXPORT int RefCuda_GetCounters( unsigned long long *out, int n );
+REF_CUDA_EXPORT unsigned long long RefCuda_LaunchCount( void );
+REF_CUDA_EXPORT const char *RefCuda_DeviceName( void );
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,285 @@
+/*
+ * rc_emu.cpp - DEBUG HARNESS, NOT A PRODUCT PATH.
+ *
+ * Implements the rc_dev.h entry points on the CPU by calling the very same scalar stage functions
+ * (xash3d-fwgs_b200/csrc/rc_core.h) the CUDA kernels call, one item at a time.  Linked with rc_host.c into
+ * tests/emu/libref_cuda_emu.so it lets the integer/float restatement of the ref_soft frame path be
+ * checked against the oracle (oracle/_ref/libref_soft.so) on a machine without a GPU.  libref_cuda.so
+ * never contains or loads this file; the GPU tests (-m gpu) exercise the kernels themselves.
+ */
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "rc_dev.h"
+#include "rc_core.h"
+
+namespace {
+struct Emu
+{
+	rc_scene_t sc{};
+	std::vector<rc_plane_t> planes; std::vector<rc_node_t> nodes; std::vector<rc_leaf_t> leafs;
+	std::vector<rc_surface_t> surfaces; std::vector<int32_t> marks, surfedges; std::vector<uint16_t> edges;
+	std::vector<float> verts; std::vector<uint8_t> visdata, lightdata;
+	std::vector<rc_texture_t> textures; std::vector<uint16_t> texels, colormap, lightgamma, cache;
+	std::vector<int32_t> sintable;
+	int32_t styles[256];
+	struct Key { int32_t texnum; int32_t light[4]; bool valid; };
+	std::vector<Key> cachekey;
+	uint64_t counters[RC_CTR_COUNT];
+	std::vector<std::vector<rc_surf_t>> vsurfs; std::vector<std::vector<rc_edge_t>> vedges;
+	uint64_t launches = 0;
+	char err[256] = "";
+} E;
+
+void fix_pointers()
+{
+	E.sc.planes = E.planes.data(); E.sc.nodes = E.nodes.data(); E.sc.leafs = E.leafs.data();
+	E.sc.surfaces = E.surfaces.data(); E.sc.marksurfaces = E.marks.data(); E.sc.surfedges = E.surfedges.data();
+	E.sc.edges = E.edges.data(); E.sc.verts = E.verts.data(); E.sc.visdata = E.visdata.data();
+	E.sc.lightdata = E.lightdata.data(); E.sc.textures = E.textures.data(); E.sc.texels = E.texels.data();
+	E.sc.colormap = E.colormap.data(); E.sc.lightgamma = E.lightgamma.data(); E.sc.sintable = E.sintable.data();
+	E.sc.cache = E.cache.data();
+	E.sc.numtextures = (int32_t)E.textures.size();
+}
+
+void build_block( int s, int mip )
+{
+	const rc_surface_t *sf = &E.surfaces[s];
+	const rc_texture_t *tex = &E.textures[sf->texnum];
+	int smax = sf->lightextents[0] / sf->sample_size + 1, tmax = sf->lightextents[1] / sf->sample_size + 1;
+	std::vector<uint32_t> bl( smax * tmax );
+	for( int i = 0; i < smax * tmax; i++ )
+		bl[i] = rc_blocklight( &E.sc, sf, E.styles, smax * tmax, i );
+	int w = sf->lightextents[0] >> mip, h = sf->lightextents[1] >> mip;
+	uint16_t *dst = E.cache.data() + sf->cache_ofs[mip];
+	for( int y = 0; y < h; y++ )
+		for( int x = 0; x < w; x++ )
+			dst[y * w + x] = rc_cache_texel( &E.sc, sf, tex, mip, bl.data(), smax, x, y );
+	Emu::Key &k = E.cachekey[s * 4 + mip];
+	k.valid = true; k.texnum = sf->texnum;
+	for( int j = 0; j < 4; j++ ) k.light[j] = sf->styles[j] != 255 ? E.styles[sf->styles[j]] : 0;
+	E.counters[RC_CTR_CACHE_BLOCKS]++; E.counters[RC_CTR_CACHE_TEXELS] += (uint64_t)w * h;
+}
+
+bool block_stale( int s, int mip )
+{
+	const rc_surface_t *sf = &E.surfaces[s];
+	const Emu::Key &k = E.cachekey[s * 4 + mip];
+	if( !k.valid || k.texnum != sf->texnum ) return true;
+	for( int j = 0; j < 4 && sf->styles[j] != 255; j++ )
+		if( k.light[j] != E.styles[sf->styles[j]] ) return true;
+	return false;
+}
+}
+
+extern "C" {
+
+int rc_dev_init( int ) { for( int i = 0; i < 256; i++ ) E.styles[i] = 256; return 0; }
+void rc_dev_shutdown( void ) {}
+const char *rc_dev_last_error( void ) { return E.err; }
+const char *rc_dev_name( void ) { return "cpu-emulation (debug harness)"; }
+uint64_t rc_dev_launch_count( void ) { return 0; }
+
+int rc_dev_upload_luts( const uint16_t *colormap, const uint16_t *lightgamma, const int32_t *sintable )
+{
+	E.colormap.assign( colormap, colormap + 32 * 8192 );
+	E.lightgamma.assign( lightgamma, lightgamma + 1024 );
+	E.sintable.assign( sintable, sintable + 1280 );
+	fix_pointers();
+	return 0;
+}
+
+int rc_dev_upload_textures( const rc_texture_t *tex, int ntex, const uint16_t *texels, size_t ntexels )
+{
+	E.textures.assign( tex, tex + ntex );
+	E.texels.assign( texels, texels + ntexels );
+	fix_pointers();
+	return rc_dev_flush_cache();
+}
+
+int rc_dev_upload_scene( const rc_scene_t *sc, size_t cache_texels )
+{
+	E.sc = *sc;
+	E.planes.assign( sc->planes, sc->planes + sc->numplanes );
+	E.nodes.assign( sc->nodes, sc->nodes + sc->numnodes );
+	E.leafs.assign( sc->leafs, sc->leafs + sc->numleafs );
+	E.surfaces.assign( sc->surfaces, sc->surfaces + sc->numsurfaces );
+	E.marks.assign( sc->marksurfaces, sc->marksurfaces + sc->nummarks );
+	E.surfedges.assign( sc->surfedges, sc->surfedges + sc->numsurfedges );
+	E.edges.assign( sc->edges, sc->edges + 2 * sc->numedges );
+	E.verts.assign( sc->verts, sc->verts + 3 * sc->numverts );
+	E.visdata.assign( sc->visdata, sc->visdata + sc->visdata_len );
+	E.lightdata.assign( sc->lightdata, sc->lightdata + sc->lightdata_len );
+	E.cache.assign( cache_texels, 0 );
+	E.cachekey.assign( (size_t)sc->numsurfaces * 4, Emu::Key{} );
+	fix_pointers();
+	return 0;
+}
+
+int rc_dev_update_surface_texnums( const int32_t *texnum, int n )
+{
+	for( int i = 0; i < n && i < (int)E.surfaces.size(); i++ ) E.surfaces[i].texnum = texnum[i];
+	return 0;
+}
+
+int rc_dev_set_lightstyles( const int32_t *values ) { memcpy( E.styles, values, sizeof( E.styles )); return 0; }
+int rc_dev_flush_cache( void ) { for( auto &k : E.cachekey ) k.valid = false; return 0; }
+
+int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, int clear, uint16_t *color_out, int16_t *z_out )
+{
+	const rc_scene_t *sc = &E.sc;
+	memset( E.counters, 0, sizeof( E.counters ));
+	E.vsurfs.assign( nviews, {} ); E.vedges.assign( nviews, {} );
+	size_t px = (size_t)width * height;
+	int stack_ints = 2 * ( sc->pad0 + 4 ) + 8;
+
+	for( int vi = 0; vi < nviews; vi++ )
+	{
+		const rc_view_t *vw = &views[vi];
+		uint16_t *color = color_out ? color_out + px * vi : nullptr;
+		int16_t *zb = z_out ? z_out + px * vi : nullptr;
+		if( clear )
+		{
+			if( color ) memset( color, 0, px * 2 );
+			if( zb ) memset( zb, 0, px * 2 );
+		}
+		/* A1 */
+		std::vector<uint8_t> vis( sc->visbytes + 8 );
+		std::vector<int32_t> stack( stack_ints + 64 );
+		if( vw->pvs_radius < 0 ) std::fill( vis.begin(), vis.end(), 0xFF );
+		else rc_fat_pvs( sc, vw->origin, vw->pvs_radius, vis.data(), stack.data(), stack_ints );
+		std::vector<uint32_t> nodevis(( sc->numnodes + 31 ) / 32 + 1 ), leafmark(( sc->numleafs + 31 ) / 32 + 1 ), surfmark(( sc->numsurfaces + 31 ) / 32 + 1 );
+		rc_mark_leaves( sc, vis.data(), nodevis.data(), leafmark.data());
+		/* A2 */
+		std::vector<rc_cand_t> cands( sc->numsurfaces + 1 );
+		int32_t overflow = 0;
+		int ncands = rc_walk_world( sc, vw, nodevis.data(), leafmark.data(), surfmark.data(), stack.data(), stack_ints, cands.data(), sc->numsurfaces, &overflow );
+		if( overflow ) E.counters[RC_CTR_OVERFLOW_STACK]++;
+		E.counters[RC_CTR_CANDS] += ncands;
+		/* A3 + A5 */
+		std::vector<rc_surf_t> surfs( ncands + 1 );
+		std::vector<rc_edge_t> edges;
+		for( int ci = 0; ci < ncands; ci++ )
+		{
+			rc_edge_t local[256];
+			rc_facestate_t fs; memset( &fs, 0, sizeof( fs ));
+			fs.out = local; fs.maxout = 256; fs.surfnum = ci + 1;
+			rc_render_face( sc, vw, &cands[ci], &fs, &surfs[ci] );
+			for( int k = 0; k < fs.nout && k < 256; k++ ) edges.push_back( local[k] );
+			if( surfs[ci].emitted )
+			{
+				E.counters[RC_CTR_SURFS]++;
+				const rc_surface_t *sf = &E.surfaces[cands[ci].surf];
+				/* A6: the block this view samples must be current */
+				if( !( sf->flags & ( RC_SURF_DRAWSKY | RC_SURF_DRAWTURB )) && sf->cache_ofs[surfs[ci].miplevel] >= 0
+					&& block_stale( cands[ci].surf, surfs[ci].miplevel ))
+					build_block( cands[ci].surf, surfs[ci].miplevel );
+			}
+		}
+		E.counters[RC_CTR_EDGES] += edges.size();
+		/* A4 + A9..A11 per scanline */
+		const int32_t *turb = E.sintable.data() + vw->turb_phase;
+		int x0 = vw->vrect[0], y0 = vw->vrect[1], vw_w = vw->vrect[2], vw_h = vw->vrect[3];
+		int32_t head_iu = x0, tail_u = (( x0 + vw_w ) << 20 ) + 0xFFFFF;
+		std::vector<rc_event_t> ev; std::vector<rc_span_t> spans( edges.size() + 2 );
+		std::vector<int32_t> stk( ncands + 2 ), cnt( ncands + 2 ), neg( 2 * 64 );
+		for( int y = y0; y < y0 + vw_h; y++ )
+		{
+			ev.clear();
+			for( const rc_edge_t &e : edges )
+				if( rc_edge_active( &e, y ))
+					ev.push_back( rc_event_t{ rc_edge_u_at( &e, y ), e.surfs } );
+			std::sort( ev.begin(), ev.end(), []( const rc_event_t &a, const rc_event_t &b ) { return rc_event_key( a.u, a.surfs ) < rc_event_key( b.u, b.surfs ); } );
+			int32_t ovf = 0;
+			int ns = rc_generate_spans( ev.data(), (int)ev.size(), head_iu, tail_u, stk.data(), cnt.data(), ncands + 1, neg.data(), 64,
+				spans.data(), (int)spans.size(), &ovf );
+			if( ovf ) E.counters[RC_CTR_OVERFLOW_EVENTS]++;
+			E.counters[RC_CTR_SPANS] += ns;
+			if( const char *dbg = getenv( "RC_EMU_DEBUG" ))
+			{
+				int dv, dx, dy;
+				if( sscanf( dbg, "%d,%d,%d", &dv, &dx, &dy ) == 3 && dv == vi && dy == y )
+				{
+					for( size_t k = 0; k < ev.size(); k++ )
+						fprintf( stderr, "ev %zu u=%d iu=%d frac=%05x trail=%u lead=%u\n", k, ev[k].u, ev[k].u >> 20, ev[k].u & 0xFFFFF, ev[k].surfs & 0xFFFF, ev[k].surfs >> 16 );
+					for( int k = 0; k < ns; k++ )
+						fprintf( stderr, "span u=%d count=%d surf=%d face=%d mip=%d\n", spans[k].u, spans[k].count, spans[k].surf, spans[k].surf ? surfs[spans[k].surf - 1].surf : -1, spans[k].surf ? surfs[spans[k].surf - 1].miplevel : -1 );
+				}
+			}
+			for( int si = 0; si < ns; si++ )
+			{
+				const rc_span_t &sp = spans[si];
+				if( !sp.surf ) continue; /* background: pixels keep their previous content */
+				const rc_surf_t *sf = &surfs[sp.surf - 1];
+				int kind = rc_span_kind( sf );
+				int nch = rc_span_nchunks( kind, sp.count ), cpx = kind == RC_KIND_TURB ? 16 : 8;
+				for( int j = 0; j < nch; j++ )
+				{
+					rc_chunk_t c;
+					rc_chunk_setup( vw, sf, vw->sky_color, sp.u, y, sp.count, j, &c );
+					int n = std::min( cpx, sp.count - j * cpx );
+					for( int i = 0; i < n; i++ )
+					{
+						size_t p = (size_t)y * width + c.u0 + i;
+						if( color )
+						{
+							if( kind == RC_KIND_SKY ) color[p] = (uint16_t)c.base;
+							else
+							{
+								int32_t ti = rc_pixel_texel( &c, i, turb );
+								color[p] = kind == RC_KIND_TURB ? E.texels[ti] : E.cache[ti];
+							}
+						}
+						if( zb ) zb[p] = rc_pixel_z( &c, i );
+					}
+				}
+			}
+		}
+		E.vsurfs[vi] = surfs; E.vedges[vi] = edges;
+		E.counters[RC_CTR_VIEWS]++; E.counters[RC_CTR_PIXELS] += (uint64_t)vw_w * vw_h;
+	}
+	return 0;
+}
+
+int rc_dev_bench_resident( int, int, float *ms_total, float *ms_stage )
+{
+	if( ms_total ) *ms_total = 0;
+	if( ms_stage ) memset( ms_stage, 0, 4 * sizeof( float ));
+	return -1;
+}
+
+int rc_dev_read_cache_block( int surf, int mip, uint16_t *out, int maxtexels, int *width, int *height, int *valid )
+{
+	if( surf < 0 || surf >= (int)E.surfaces.size() || mip < 0 || mip > 3 ) return -1;
+	const rc_surface_t *sf = &E.surfaces[surf];
+	int w = sf->lightextents[0] >> mip, h = sf->lightextents[1] >> mip;
+	*width = w; *height = h;
+	*valid = sf->cache_ofs[mip] >= 0 && E.cachekey[surf * 4 + mip].valid && !block_stale( surf, mip );
+	if( *valid && w * h <= maxtexels )
+		memcpy( out, E.cache.data() + sf->cache_ofs[mip], (size_t)w * h * 2 );
+	return 0;
+}
+
+int rc_dev_read_counters( uint64_t *out, int n ) { for( int i = 0; i < n && i < RC_CTR_COUNT; i++ ) out[i] = E.counters[i]; return 0; }
+
+int rc_dev_read_view_surfs( int view, rc_surf_t *out, int max, int *n )
+{
+	if( view < 0 || view >= (int)E.vsurfs.size()) return -1;
+	*n = (int)E.vsurfs[view].size() - 1;
+	for( int i = 0; i < *n && i < max; i++ ) out[i] = E.vsurfs[view][i];
+	return 0;
+}
+
+int rc_dev_read_view_edges( int view, rc_edge_t *out, int max, int *n )
+{
+	if( view < 0 || view >= (int)E.vedges.size()) return -1;
+	*n = (int)E.vedges[view].size();
+	for( int i = 0; i < *n && i < max; i++ ) out[i] = E.vedges[view][i];
+	return 0;
+}
+
+}

@@ -1,0 +1,912 @@
+/*
+ * rc_core.h - the per-item arithmetic of the ref_cuda frame path, written once as scalar
+ * __host__ __device__ functions.  The CUDA kernels in rc_device.cu supply the parallel
+ * decomposition (warp per view, thread per face, warp per scanline, thread per texel) around
+ * these; tests/emu/ compiles the very same functions with g++ to debug integer parity against
+ * the oracle on a box without a GPU (debug harness only - libref_cuda.so contains no CPU path).
+ *
+ * Float rule: every float expression keeps the reference's operand order and is compiled
+ * without FMA contraction (nvcc -fmad=false, IEEE div/sqrt), matching the oracle's plain
+ * gcc -O2 x86-64 SSE build (oracle/Makefile).  float->int uses rc_f2i (x86 cvttss2si
+ * semantics incl. the 0x80000000 overflow result).
+ */
+#ifndef RC_CORE_H
+#define RC_CORE_H
+
+#include "rc_shared.h"
+
+#if defined( __CUDACC__ )
+#define RC_HD __host__ __device__ __forceinline__
+#define RC_HD_NOINLINE __host__ __device__ __noinline__
+#else
+#define RC_HD static inline
+#define RC_HD_NOINLINE static
+#endif
+
+#define RC_NEAR_CLIP        0.01f  /* ref/soft/r_local.h:626 */
+#define RC_BACKFACE_EPSILON 0.01   /* double constant, ref/soft/r_local.h */
+#define RC_CYCLE            128    /* ref/soft/r_local.h:595 */
+#define RC_BACKGROUND_KEY   0x7FFFFFFF
+
+/* (int)f with x86-64 cvttss2si semantics: out-of-range and NaN give INT_MIN */
+RC_HD int32_t rc_f2i( float f )
+{
+	if( !( f > -2147483904.0f && f < 2147483648.0f ))
+		return (int32_t)0x80000000;
+	return (int32_t)f;
+}
+
+RC_HD float rc_dot3( const float *a, const float *b )
+{
+	return a[0] * b[0] + a[1] * b[1] + a[2] * b[2];
+}
+
+/* TransformVector, ref/soft/r_misc.c:127 */
+RC_HD void rc_transform( const rc_view_t *vw, const float *in, float *out )
+{
+	out[0] = rc_dot3( in, vw->vright );
+	out[1] = rc_dot3( in, vw->vup );
+	out[2] = rc_dot3( in, vw->vforward );
+}
+
+/* PlaneDiff, public/xash3d_mathlib.h:143 */
+RC_HD float rc_planediff( const float *p, const rc_plane_t *pl )
+{
+	return ( pl->type < 3 ? p[pl->type] : rc_dot3( p, pl->normal )) - pl->dist;
+}
+
+/* ------------------------------------------------------------------------------------------ */
+/* A1: view leaf, fat PVS, leaf->parent marking                                                 */
+
+/* Mod_PointInLeaf, engine/common/mod_bmodel.c:1116: "<= 0" takes the back child */
+RC_HD int32_t rc_point_in_leaf( const rc_scene_t *sc, const float *p )
+{
+	int32_t n = sc->headnode;
+	while( n >= 0 )
+	{
+		const rc_node_t *node = &sc->nodes[n];
+		n = node->child[rc_planediff( p, &sc->planes[node->plane] ) <= 0 ? 1 : 0];
+	}
+	return -1 - n;
+}
+
+/* Mod_DecompressPVS (mod_bmodel.c:1054) fused with Q_memor: OR one leaf's zero-run RLE row into out */
+RC_HD void rc_pvs_or_row( const rc_scene_t *sc, int32_t visofs, uint8_t *out )
+{
+	int32_t n = sc->visbytes, d = 0;
+	if( visofs < 0 )
+	{
+		for( d = 0; d < n; d++ ) out[d] = 0xFF;
+		return;
+	}
+	const uint8_t *in = sc->visdata + visofs;
+	while( d < n )
+	{
+		if( *in )
+			out[d++] |= *in++;
+		else
+		{
+			d += in[1];
+			in += 2;
+		}
+	}
+}
+
+/* Mod_FatPVS (mod_bmodel.c:1203) with merge = fullvis = phs = false, as R_MarkLeaves calls it
+ * (ref/soft/r_main.c:1030).  stack: scratch ints for the both-sides recursion. */
+RC_HD void rc_fat_pvs( const rc_scene_t *sc, const float *org, float radius, uint8_t *out, int32_t *stack, int32_t stackcap )
+{
+	int32_t n = sc->visbytes;
+	int32_t leaf = rc_point_in_leaf( sc, org );
+
+	if( !sc->visdata_len || sc->leafs[leaf].cluster < 0 )
+	{
+		for( int32_t i = 0; i < n; i++ ) out[i] = 0xFF;
+		return;
+	}
+	for( int32_t i = 0; i < n; i++ ) out[i] = 0;
+
+	int32_t sp = 0;
+	int32_t node = sc->headnode;
+	for( ;; )
+	{
+		while( node >= 0 )
+		{
+			const rc_node_t *nd = &sc->nodes[node];
+			float d = rc_planediff( org, &sc->planes[nd->plane] );
+			if( d > radius ) node = nd->child[0];
+			else if( d < -radius ) node = nd->child[1];
+			else
+			{
+				/* go down both sides: front first, back deferred */
+				if( sp < stackcap ) stack[sp++] = nd->child[1];
+				node = nd->child[0];
+			}
+		}
+		const rc_leaf_t *lf = &sc->leafs[-1 - node];
+		if( lf->cluster >= 0 )
+			rc_pvs_or_row( sc, lf->visofs, out );
+		if( !sp ) break;
+		node = stack[--sp];
+	}
+}
+
+RC_HD int rc_testbit( const uint32_t *w, int32_t i ) { return ( w[i >> 5] >> ( i & 31 )) & 1; }
+RC_HD void rc_setbit( uint32_t *w, int32_t i ) { w[i >> 5] |= 1u << ( i & 31 ); }
+
+/* R_MarkLeaves, ref/soft/r_main.c:1021-1047: for every PVS bit stamp the leaf and its parent chain */
+RC_HD void rc_mark_leaves( const rc_scene_t *sc, const uint8_t *vis, uint32_t *nodevis, uint32_t *leafmark )
+{
+	for( int32_t i = 0; i < sc->numclusters; i++ )
+	{
+		if( !( vis[i >> 3] & ( 1 << ( i & 7 ))))
+			continue;
+		rc_setbit( leafmark, i + 1 );
+		int32_t node = sc->leafs[i + 1].parent;
+		while( node >= 0 && !rc_testbit( nodevis, node ))
+		{
+			rc_setbit( nodevis, node );
+			node = sc->nodes[node].parent;
+		}
+	}
+}
+
+/* ------------------------------------------------------------------------------------------ */
+/* A2: front-to-back BSP walk                                                                   */
+
+/* the 4-plane bbox test of R_RecursiveWorldNode (ref/soft/r_bsp.c:483-520); returns -1 when rejected,
+ * else the reduced clipflags.  d is a double there, but ( (double)dotf - (double)dist ) has the sign of
+ * the exact difference, so comparing the float dot against dist decides identically. */
+RC_HD int32_t rc_cull_box( const rc_view_t *vw, const float *minmaxs, int32_t clipflags )
+{
+	for( int i = 0; i < 4; i++ )
+	{
+		if( !( clipflags & ( 1 << i )))
+			continue;
+		const int32_t *pindex = vw->frustum_idx[i];
+		float pt[3];
+		pt[0] = minmaxs[pindex[0]]; pt[1] = minmaxs[pindex[1]]; pt[2] = minmaxs[pindex[2]];
+		double d = (double)rc_dot3( pt, vw->clip_normal[i] );
+		d -= (double)vw->clip_dist[i];
+		if( d <= 0 )
+			return -1;
+		pt[0] = minmaxs[pindex[3]]; pt[1] = minmaxs[pindex[4]]; pt[2] = minmaxs[pindex[5]];
+		d = (double)rc_dot3( pt, vw->clip_normal[i] );
+		d -= (double)vw->clip_dist[i];
+		if( d >= 0 )
+			clipflags &= ~( 1 << i );
+	}
+	return clipflags;
+}
+
+/* which side of a node plane the eye is on (r_bsp.c:550-571); float arithmetic, widened for the compares */
+RC_HD double rc_node_dot( const rc_view_t *vw, const rc_plane_t *pl )
+{
+	float dotf;
+	switch( pl->type )
+	{
+	case 0: dotf = vw->origin[0] - pl->dist; break;
+	case 1: dotf = vw->origin[1] - pl->dist; break;
+	case 2: dotf = vw->origin[2] - pl->dist; break;
+	default: dotf = rc_dot3( vw->origin, pl->normal ) - pl->dist; break;
+	}
+	return (double)dotf;
+}
+
+/*
+ * R_RenderWorld / R_RecursiveWorldNode (ref/soft/r_bsp.c:466-641) with the recursion unrolled onto an
+ * explicit stack.  Output: the faces R_RenderFace would be called with, in call order (== ascending
+ * surf_t.key order), each with its clipflags.  Keys: the reference bumps r_currentkey per posted face,
+ * per node with surfaces and per leaf; only the order matters to the span generator, so the candidate
+ * index is the key here (a strictly monotone relabelling).
+ * stack entry = 2 ints: node ref, (clipflags | stage << 4).
+ */
+RC_HD int32_t rc_walk_world( const rc_scene_t *sc, const rc_view_t *vw, const uint32_t *nodevis, const uint32_t *leafmark,
+	uint32_t *surfmark, int32_t *stack, int32_t stack_ints, rc_cand_t *cands, int32_t max_cands, int32_t *overflow )
+{
+	int32_t ncands = 0, sp = 0;
+	stack[sp++] = sc->headnode; stack[sp++] = 15;
+
+	while( sp )
+	{
+		int32_t st = stack[--sp];
+		int32_t ref = stack[--sp];
+		int32_t clipflags = st & 15;
+
+		if( st & 16 )
+		{
+			/* second visit of a node: draw its faces, then descend the back side */
+			const rc_node_t *node = &sc->nodes[ref];
+			double dot = rc_node_dot( vw, &sc->planes[node->plane] );
+			int side = dot >= 0 ? 0 : 1;
+			int32_t c = node->numsurfaces;
+			if( c )
+			{
+				int want;
+				if( dot < -RC_BACKFACE_EPSILON ) want = 1;
+				else if( dot > RC_BACKFACE_EPSILON ) want = 0;
+				else want = -1;
+				if( want >= 0 )
+				{
+					for( int32_t s = node->firstsurface; s < node->firstsurface + c; s++ )
+					{
+						int back = ( sc->surfaces[s].flags & RC_SURF_PLANEBACK ) ? 1 : 0;
+						if( back == want && rc_testbit( surfmark, s ))
+						{
+							if( ncands < max_cands )
+							{
+								cands[ncands].surf = s;
+								cands[ncands].clipflags = clipflags;
+								ncands++;
+							}
+							else *overflow = 1;
+						}
+					}
+				}
+			}
+			stack[sp++] = node->child[!side]; stack[sp++] = clipflags;
+			continue;
+		}
+
+		if( ref < 0 )
+		{
+			int32_t li = -1 - ref;
+			const rc_leaf_t *leaf = &sc->leafs[li];
+			if( leaf->contents == RC_CONTENTS_SOLID || !rc_testbit( leafmark, li ))
+				continue;
+			if( clipflags && rc_cull_box( vw, leaf->minmaxs, clipflags ) < 0 )
+				continue;
+			for( int32_t m = leaf->firstmark; m < leaf->firstmark + leaf->nummark; m++ )
+				rc_setbit( surfmark, sc->marksurfaces[m] );
+			continue;
+		}
+
+		const rc_node_t *node = &sc->nodes[ref];
+		if( !rc_testbit( nodevis, ref ))
+			continue;
+		if( clipflags )
+		{
+			clipflags = rc_cull_box( vw, node->minmaxs, clipflags );
+			if( clipflags < 0 )
+				continue;
+		}
+		double dot = rc_node_dot( vw, &sc->planes[node->plane] );
+		int side = dot >= 0 ? 0 : 1;
+		if( sp + 4 > stack_ints ) { *overflow = 1; continue; }
+		stack[sp++] = ref; stack[sp++] = clipflags | 16;
+		stack[sp++] = node->child[side]; stack[sp++] = clipflags;
+	}
+	return ncands;
+}
+
+/* ------------------------------------------------------------------------------------------ */
+/* A3: R_RenderFace / R_ClipEdge / R_EmitEdge (ref/soft/r_rast.c:63-584)                        */
+
+typedef struct
+{
+	/* statics of r_rast.c that live across the edges of one face */
+	int     lastvertvalid, emitted, nearzionly;
+	int     leftclipped, rightclipped;
+	float   nearzi;
+	float   u1, v1, lzi1;
+	int32_t ceilv1;
+	float   leftenter[3], leftexit[3], rightenter[3], rightexit[3];
+	/* output */
+	rc_edge_t *out;
+	int32_t nout, maxout;
+	uint32_t surfnum; /* candidate index + 1 */
+} rc_facestate_t;
+
+RC_HD void rc_project( const rc_view_t *vw, const float *world, float *pu, float *pv, float *plzi )
+{
+	float local[3], tv[3];
+	local[0] = world[0] - vw->origin[0];
+	local[1] = world[1] - vw->origin[1];
+	local[2] = world[2] - vw->origin[2];
+	rc_transform( vw, local, tv );
+	if( tv[2] < RC_NEAR_CLIP )
+		tv[2] = RC_NEAR_CLIP;
+	float lzi = 1.0f / tv[2];
+	float scale = vw->xscale * lzi;
+	float u = ( vw->xcenter + scale * tv[0] );
+	if( u < vw->fvrectx_adj ) u = vw->fvrectx_adj;
+	if( u > vw->fvrectright_adj ) u = vw->fvrectright_adj;
+	scale = vw->yscale * lzi;
+	float v = ( vw->ycenter - scale * tv[1] );
+	if( v < vw->fvrecty_adj ) v = vw->fvrecty_adj;
+	if( v > vw->fvrectbottom_adj ) v = vw->fvrectbottom_adj;
+	*pu = u; *pv = v; *plzi = lzi;
+}
+
+/* R_EmitEdge, r_rast.c:63-253.  The newedges[]/removeedges[] bucket insertion is replaced by the
+ * flat per-view edge array; the scanline kernel sorts by u itself. */
+RC_HD void rc_emit_edge( const rc_view_t *vw, rc_facestate_t *fs, const float *p0, const float *p1 )
+{
+	float u0, v0, lzi0;
+	int32_t ceilv0;
+
+	if( fs->lastvertvalid )
+	{
+		u0 = fs->u1; v0 = fs->v1; lzi0 = fs->lzi1; ceilv0 = fs->ceilv1;
+	}
+	else
+	{
+		rc_project( vw, p0, &u0, &v0, &lzi0 );
+		ceilv0 = (int32_t)ceilf( v0 );
+	}
+
+	rc_project( vw, p1, &fs->u1, &fs->v1, &fs->lzi1 );
+
+	if( fs->lzi1 > lzi0 ) lzi0 = fs->lzi1;
+	if( lzi0 > fs->nearzi ) fs->nearzi = lzi0;
+
+	if( fs->nearzionly )
+		return;
+
+	fs->emitted = 1;
+	fs->ceilv1 = (int32_t)ceilf( fs->v1 );
+
+	if( ceilv0 == fs->ceilv1 || ceilv0 < 0 )
+		return; /* horizontal edge */
+
+	int side = ceilv0 > fs->ceilv1;
+	int32_t v, v2;
+	float u, u_step;
+	uint32_t surfs;
+
+	if( side == 0 )
+	{
+		/* trailing edge (go from p1 to p2) */
+		v = ceilv0; v2 = fs->ceilv1 - 1;
+		surfs = fs->surfnum;
+		u_step = (( fs->u1 - u0 ) / ( fs->v1 - v0 ));
+		u = u0 + ((float)v - v0 ) * u_step;
+	}
+	else
+	{
+		/* leading edge (go from p2 to p1) */
+		v2 = ceilv0 - 1; v = fs->ceilv1;
+		surfs = fs->surfnum << 16;
+		u_step = (( u0 - fs->u1 ) / ( v0 - fs->v1 ));
+		u = fs->u1 + ((float)v - fs->v1 ) * u_step;
+	}
+	if( v < 0 || v >= 1200 ) /* MAXHEIGHT */
+		return;
+
+	int32_t iustep = rc_f2i( u_step * (float)0x100000 );
+	int32_t iu = rc_f2i( u * (float)0x100000 + (float)0xFFFFF );
+	if( iu < vw->vrect_x_adj_shift20 ) iu = vw->vrect_x_adj_shift20;
+	if( iu > vw->vrectright_adj_shift20 ) iu = vw->vrectright_adj_shift20;
+
+	if( fs->nout < fs->maxout )
+	{
+		rc_edge_t *e = &fs->out[fs->nout];
+		e->u = iu; e->u_step = iustep;
+		e->vv = (uint32_t)v | ((uint32_t)v2 << 16 );
+		e->surfs = surfs;
+	}
+	fs->nout++;
+}
+
+/* R_ClipEdge, r_rast.c:261-352: the tail recursion over the clip-plane list becomes a loop */
+RC_HD void rc_clip_edge( const rc_view_t *vw, rc_facestate_t *fs, const float *pv0, const float *pv1, const int *planes, int nplanes, int kstart )
+{
+	float a[3], b[3];
+	a[0] = pv0[0]; a[1] = pv0[1]; a[2] = pv0[2];
+	b[0] = pv1[0]; b[1] = pv1[1]; b[2] = pv1[2];
+
+	for( int k = kstart; k < nplanes; k++ )
+	{
+		int pl = planes[k];
+		float d0 = rc_dot3( a, vw->clip_normal[pl] ) - vw->clip_dist[pl];
+		float d1 = rc_dot3( b, vw->clip_normal[pl] ) - vw->clip_dist[pl];
+
+		if( d0 >= 0 )
+		{
+			if( d1 >= 0 )
+				continue;
+			/* only point 1 is clipped */
+			float f = d0 / ( d0 - d1 );
+			float c[3];
+			c[0] = a[0] + f * ( b[0] - a[0] );
+			c[1] = a[1] + f * ( b[1] - a[1] );
+			c[2] = a[2] + f * ( b[2] - a[2] );
+			if( pl == 0 ) { fs->leftclipped = 1; fs->leftexit[0] = c[0]; fs->leftexit[1] = c[1]; fs->leftexit[2] = c[2]; }
+			else if( pl == 1 ) { fs->rightclipped = 1; fs->rightexit[0] = c[0]; fs->rightexit[1] = c[1]; fs->rightexit[2] = c[2]; }
+			b[0] = c[0]; b[1] = c[1]; b[2] = c[2];
+		}
+		else
+		{
+			if( d1 < 0 )
+				return; /* both points are clipped */
+			/* only point 0 is clipped */
+			fs->lastvertvalid = 0;
+			float f = d0 / ( d0 - d1 );
+			float c[3];
+			c[0] = a[0] + f * ( b[0] - a[0] );
+			c[1] = a[1] + f * ( b[1] - a[1] );
+			c[2] = a[2] + f * ( b[2] - a[2] );
+			if( pl == 0 ) { fs->leftclipped = 1; fs->leftenter[0] = c[0]; fs->leftenter[1] = c[1]; fs->leftenter[2] = c[2]; }
+			else if( pl == 1 ) { fs->rightclipped = 1; fs->rightenter[0] = c[0]; fs->rightenter[1] = c[1]; fs->rightenter[2] = c[2]; }
+			a[0] = c[0]; a[1] = c[1]; a[2] = c[2];
+		}
+	}
+	rc_emit_edge( vw, fs, a, b );
+}
+
+/* D_MipLevelForScale, ref/soft/r_edge.c:697-714 */
+RC_HD int32_t rc_miplevel_for_scale( const rc_view_t *vw, float scale )
+{
+	int32_t lmiplevel;
+	if( scale >= vw->scalemip[0] ) lmiplevel = 0;
+	else if( scale >= vw->scalemip[1] ) lmiplevel = 1;
+	else if( scale >= vw->scalemip[2] ) lmiplevel = 2;
+	else lmiplevel = 3;
+	if( lmiplevel < vw->minmip ) lmiplevel = vw->minmip;
+	return lmiplevel;
+}
+
+/* D_CalcGradients, ref/soft/r_edge.c:741-813 (non-conveyor, non-TEX_WORLD_LUXELS faces) */
+RC_HD void rc_calc_gradients( const rc_view_t *vw, const rc_surface_t *sf, int32_t miplevel, rc_surf_t *o )
+{
+	float p_saxis[3], p_taxis[3], p_temp1[3];
+	float mipscale = 1.0f / (float)( 1 << miplevel );
+
+	rc_transform( vw, sf->lmvecs[0], p_saxis );
+	rc_transform( vw, sf->lmvecs[1], p_taxis );
+
+	float t = vw->xscaleinv * mipscale;
+	o->d_sdivzstepu = p_saxis[0] * t;
+	o->d_tdivzstepu = p_taxis[0] * t;
+
+	t = vw->yscaleinv * mipscale;
+	o->d_sdivzstepv = -p_saxis[1] * t;
+	o->d_tdivzstepv = -p_taxis[1] * t;
+
+	o->d_sdivzorigin = p_saxis[2] * mipscale - vw->xcenter * o->d_sdivzstepu - vw->ycenter * o->d_sdivzstepv;
+	o->d_tdivzorigin = p_taxis[2] * mipscale - vw->xcenter * o->d_tdivzstepu - vw->ycenter * o->d_tdivzstepv;
+
+	p_temp1[0] = vw->modelorg_t[0] * mipscale;
+	p_temp1[1] = vw->modelorg_t[1] * mipscale;
+	p_temp1[2] = vw->modelorg_t[2] * mipscale;
+
+	t = (float)0x10000 * mipscale;
+	/* int - int + float: the sum is taken in float, then truncated on assignment (fixed16_t) */
+	o->sadjust = rc_f2i((float)( rc_f2i( rc_dot3( p_temp1, p_saxis ) * (float)0x10000 + 0.5f )
+		- (((int32_t)sf->lightmapmins[0] << 16 ) >> miplevel )) + sf->lmvecs[0][3] * t );
+	o->tadjust = rc_f2i((float)( rc_f2i( rc_dot3( p_temp1, p_taxis ) * (float)0x10000 + 0.5f )
+		- (((int32_t)sf->lightmapmins[1] << 16 ) >> miplevel )) + sf->lmvecs[1][3] * t );
+
+	o->bbextents = (((int32_t)sf->lightextents[0] << 16 ) >> miplevel ) - 1;
+	o->bbextentt = (((int32_t)sf->lightextents[1] << 16 ) >> miplevel ) - 1;
+}
+
+/*
+ * R_RenderFace (r_rast.c:384-586) for a world face + the per-surface part of D_SolidSurf /
+ * D_TurbulentSurf / D_BackgroundSurf (r_edge.c:823-1053).  Edges go to fs->out (count in fs->nout,
+ * which may exceed maxout: the caller treats that as overflow).  The shared-edge cache
+ * (medge16_t.cachededgeoffset) is not reproduced: an edge computed twice gives bit-identical
+ * values because (a-b)/(c-d) == (b-a)/(d-c) in IEEE arithmetic.
+ */
+RC_HD void rc_render_face( const rc_scene_t *sc, const rc_view_t *vw, const rc_cand_t *cand, rc_facestate_t *fs, rc_surf_t *o )
+{
+	const rc_surface_t *sf = &sc->surfaces[cand->surf];
+	int planes[4], nplanes = 0;
+	for( int i = 0; i < 4; i++ )
+		if( cand->clipflags & ( 1 << i ))
+			planes[nplanes++] = i;
+
+	fs->emitted = 0; fs->nearzi = 0; fs->nearzionly = 0; fs->lastvertvalid = 0;
+	fs->u1 = fs->v1 = fs->lzi1 = 0; fs->ceilv1 = 0;
+	int makeleftedge = 0, makerightedge = 0;
+
+	for( int32_t i = 0; i < sf->numedges; i++ )
+	{
+		int32_t lindex = sc->surfedges[sf->firstedge + i];
+		const float *v0, *v1;
+		if( lindex > 0 )
+		{
+			v0 = sc->verts + 3 * sc->edges[2 * lindex];
+			v1 = sc->verts + 3 * sc->edges[2 * lindex + 1];
+		}
+		else
+		{
+			lindex = -lindex;
+			v0 = sc->verts + 3 * sc->edges[2 * lindex + 1];
+			v1 = sc->verts + 3 * sc->edges[2 * lindex];
+		}
+		fs->leftclipped = fs->rightclipped = 0;
+		rc_clip_edge( vw, fs, v0, v1, planes, nplanes, 0 );
+		if( fs->leftclipped ) makeleftedge = 1;
+		if( fs->rightclipped ) makerightedge = 1;
+		fs->lastvertvalid = 1;
+	}
+
+	/* if there was a clip off the left edge, add that edge too (pclip->next: skip the left plane) */
+	if( makeleftedge )
+	{
+		fs->lastvertvalid = 0;
+		rc_clip_edge( vw, fs, fs->leftexit, fs->leftenter, planes, nplanes, 1 );
+	}
+	/* if there was a clip off the right edge, get the right r_nearzi (view_clipplanes[1].next) */
+	if( makerightedge )
+	{
+		fs->lastvertvalid = 0;
+		fs->nearzionly = 1;
+		int k = 0;
+		while( k < nplanes && planes[k] <= 1 ) k++;
+		rc_clip_edge( vw, fs, fs->rightexit, fs->rightenter, planes, nplanes, k );
+	}
+
+	o->surf = cand->surf;
+	o->flags = sf->flags;
+	o->emitted = fs->emitted;
+	o->nearzi = fs->nearzi;
+	if( !fs->emitted )
+		return;
+
+	const rc_plane_t *pl = &sc->planes[sf->plane];
+	float p_normal[3];
+	rc_transform( vw, pl->normal, p_normal );
+	float distinv = 1.0f / ( pl->dist - rc_dot3( vw->origin, pl->normal ));
+	o->d_zistepu = p_normal[0] * vw->xscaleinv * distinv;
+	o->d_zistepv = -p_normal[1] * vw->yscaleinv * distinv;
+	o->d_ziorigin = p_normal[2] * distinv - vw->xcenter * o->d_zistepu - vw->ycenter * o->d_zistepv;
+
+	if( sf->flags & RC_SURF_DRAWSKY )
+	{
+		/* D_BackgroundSurf: flat fill at "infinity" */
+		o->d_zistepu = 0; o->d_zistepv = 0; o->d_ziorigin = -0.9f;
+		o->miplevel = 0; o->cache_ofs = -1; o->cachewidth = 0;
+		return;
+	}
+	if( sf->flags & RC_SURF_DRAWTURB )
+	{
+		/* D_TurbulentSurf: mip 0 of the 64x64 texture itself, no cache */
+		o->miplevel = 0;
+		o->cache_ofs = sc->textures[sf->texnum].ofs[0];
+		o->cachewidth = 64;
+		rc_calc_gradients( vw, sf, 0, o );
+		return;
+	}
+
+	int32_t miplevel = rc_miplevel_for_scale( vw, fs->nearzi * vw->scale_for_mip );
+	while(( 1 << miplevel ) > sf->sample_size )
+		miplevel--;
+	o->miplevel = miplevel;
+	o->cache_ofs = sf->cache_ofs[miplevel];
+	o->cachewidth = (int32_t)sf->lightextents[0] >> miplevel;
+	rc_calc_gradients( vw, sf, miplevel, o );
+}
+
+/* ------------------------------------------------------------------------------------------ */
+/* A4: span generation for one scanline (ref/soft/r_edge.c:360-583)                             */
+
+typedef struct { int32_t u; uint32_t surfs; } rc_event_t; /* an active edge at this scanline */
+typedef struct { int32_t u, count, surf; } rc_span_t;     /* surf: 0 = background, else candidate index + 1 */
+
+/* edge->u after (y - v) executions of "edge->u += edge->u_step" (R_StepActiveU, r_edge.c:187): int32 wraparound */
+RC_HD int32_t rc_edge_u_at( const rc_edge_t *e, int32_t y )
+{
+	uint32_t v = e->vv & 0xFFFF;
+	return (int32_t)((uint32_t)e->u + ((uint32_t)y - v ) * (uint32_t)e->u_step );
+}
+
+RC_HD int rc_edge_active( const rc_edge_t *e, int32_t y )
+{
+	int32_t v = (int32_t)( e->vv & 0xFFFF ), v2 = (int32_t)( e->vv >> 16 );
+	return y >= v && y <= v2;
+}
+
+/* total order the active edge table is kept in: by u; ties (which only arise for edges clamped to a
+ * screen border or for the two copies of a shared edge) broken so that the result is deterministic */
+RC_HD uint64_t rc_event_key( int32_t u, uint32_t surfs )
+{
+	return ((uint64_t)((uint32_t)u ^ 0x80000000u ) << 32 ) | surfs;
+}
+
+/*
+ * R_GenerateSpans + R_LeadingEdge + R_TrailingEdge + R_CleanupSpan for one scanline, events sorted by u.
+ * The key-ordered surf_t stack is a sorted array (world keys are unique and equal the candidate
+ * order); spanstate (r_edge.c:405,366) is kept as a count per stack entry plus a short list of
+ * "inverted" surfaces whose trailing edge came first.
+ * stk/cnt: scratch of stkcap entries; neg: scratch of 2*negcap ints.
+ * Returns the number of spans written (spans of surf 0 = background are written too).
+ */
+RC_HD int32_t rc_generate_spans( const rc_event_t *ev, int32_t nev, int32_t head_iu, int32_t tail_u,
+	int32_t *stk, int32_t *cnt, int32_t stkcap, int32_t *neg, int32_t negcap, rc_span_t *spans, int32_t maxspans, int32_t *overflow )
+{
+	int32_t depth = 0, nneg = 0, nspans = 0;
+	int32_t top = 0, top_last_u = head_iu; /* surfaces[1].last_u = edge_head_u_shift20 */
+
+#define RC_EMIT_SPAN( SURF, LAST, IU ) \
+	if(( IU ) > ( LAST )) { if( nspans < maxspans ) { spans[nspans].u = ( LAST ); spans[nspans].count = ( IU ) - ( LAST ); spans[nspans].surf = ( SURF ); nspans++; } else *overflow = 1; }
+
+	for( int32_t e = 0; e < nev; e++ )
+	{
+		int32_t u = ev[e].u;
+		if( u > tail_u )
+			break; /* sorted past edge_tail: R_GenerateSpans stops there */
+		int32_t iu = u >> 20;
+		int32_t trail = (int32_t)( ev[e].surfs & 0xFFFF ), lead = (int32_t)( ev[e].surfs >> 16 );
+
+		if( trail )
+		{
+			/* R_TrailingEdge: --spanstate == 0 -> leave the stack */
+			int32_t i;
+			for( i = 0; i < depth; i++ ) if( stk[i] == trail ) break;
+			if( i < depth )
+			{
+				if( --cnt[i] == 0 )
+				{
+					if( i == 0 )
+					{
+						RC_EMIT_SPAN( trail, top_last_u, iu )
+						top_last_u = iu; /* surf->next->last_u = iu */
+					}
+					for( int32_t k = i; k + 1 < depth; k++ ) { stk[k] = stk[k + 1]; cnt[k] = cnt[k + 1]; }
+					depth--;
+					top = depth ? stk[0] : 0;
+				}
+			}
+			else
+			{
+				/* inverted span: spanstate goes negative */
+				for( i = 0; i < nneg; i++ ) if( neg[2 * i] == trail ) break;
+				if( i < nneg ) neg[2 * i + 1]--;
+				else if( nneg < negcap ) { neg[2 * nneg] = trail; neg[2 * nneg + 1] = -1; nneg++; }
+				else *overflow = 1;
+			}
+		}
+		if( lead )
+		{
+			/* R_LeadingEdge: ++spanstate == 1 -> enter the stack at its key position */
+			int32_t i;
+			for( i = 0; i < nneg; i++ ) if( neg[2 * i] == lead ) break;
+			if( i < nneg )
+			{
+				if( ++neg[2 * i + 1] == 0 ) { neg[2 * i] = neg[2 * ( nneg - 1 )]; neg[2 * i + 1] = neg[2 * ( nneg - 1 ) + 1]; nneg--; }
+				continue;
+			}
+			for( i = 0; i < depth; i++ ) if( stk[i] >= lead ) break;
+			if( i < depth && stk[i] == lead ) { cnt[i]++; continue; }
+			if( depth >= stkcap ) { *overflow = 1; continue; }
+			if( i == 0 )
+			{
+				/* newtop: emit a span for the surface being obscured */
+				RC_EMIT_SPAN( top, top_last_u, iu )
+				top_last_u = iu;
+			}
+			for( int32_t k = depth; k > i; k-- ) { stk[k] = stk[k - 1]; cnt[k] = cnt[k - 1]; }
+			stk[i] = lead; cnt[i] = 1; depth++;
+			top = stk[0];
+		}
+	}
+	/* R_CleanupSpan: whatever is on top runs to the right edge */
+	{
+		int32_t iu = tail_u >> 20;
+		RC_EMIT_SPAN( top, top_last_u, iu )
+	}
+#undef RC_EMIT_SPAN
+	return nspans;
+}
+
+/* ------------------------------------------------------------------------------------------ */
+/* A9/A10/A11: span drawing split into chunk set-up (float, once per 8 or 16 pixels) and the    */
+/* per-pixel integer part (ref/soft/r_scan.c:89-221,528-668,1309-1357)                          */
+
+enum { RC_KIND_BACKGROUND = 0, RC_KIND_SOLID = 1, RC_KIND_TURB = 2, RC_KIND_SKY = 3 };
+
+typedef struct
+{
+	int32_t s, t, sstep, tstep; /* 16.16 texture coordinates at the chunk's first pixel + per-pixel step */
+	int32_t izi, izistep;       /* 1/z (<<31) at the chunk's first pixel + per-pixel step */
+	int32_t base, width;        /* texel offset and row pitch of the cache block / texture; sky: base = colour */
+	int32_t u0, kind;
+} rc_chunk_t; /* 40 B */
+
+RC_HD int32_t rc_span_kind( const rc_surf_t *sf )
+{
+	if( sf->flags & RC_SURF_DRAWSKY ) return RC_KIND_SKY;
+	if( sf->flags & RC_SURF_DRAWTURB ) return RC_KIND_TURB;
+	return RC_KIND_SOLID;
+}
+
+RC_HD int32_t rc_span_nchunks( int32_t kind, int32_t count )
+{
+	return kind == RC_KIND_TURB ? ( count + 15 ) >> 4 : ( count + 7 ) >> 3;
+}
+
+RC_HD int32_t rc_clamp_st( int32_t x, int32_t hi, int32_t lo )
+{
+	if( x > hi ) x = hi;
+	else if( x < lo ) x = lo;
+	return x;
+}
+
+/*
+ * State of D_DrawSpans16 / Turbulent8 at the start of chunk j of a span (u, v, count).  The reference
+ * walks the chunks sequentially accumulating sdivz/tdivz/zi in float; chunk j repeats those j additions
+ * so that chunks can be set up independently (one lane each) with bit-identical results.
+ */
+RC_HD void rc_chunk_setup( const rc_view_t *vw, const rc_surf_t *sf, int32_t sky_color, int32_t u, int32_t v, int32_t count, int32_t j, rc_chunk_t *c )
+{
+	int32_t kind = rc_span_kind( sf );
+	int32_t px = kind == RC_KIND_TURB ? 16 : 8;
+	float du = (float)u, dv = (float)v;
+
+	/* D_DrawZSpans: closed form per pixel */
+	float zi = sf->d_ziorigin + dv * sf->d_zistepv + du * sf->d_zistepu;
+	int32_t izistep = rc_f2i( sf->d_zistepu * (float)0x8000 * (float)0x10000 );
+	int32_t izi0 = rc_f2i( zi * (float)0x8000 * (float)0x10000 );
+	c->izistep = izistep;
+	c->izi = (int32_t)((uint32_t)izi0 + (uint32_t)( j * px ) * (uint32_t)izistep );
+	c->u0 = u + j * px;
+	c->kind = kind;
+	c->base = sf->cache_ofs;
+	c->width = sf->cachewidth;
+	c->s = c->t = c->sstep = c->tstep = 0;
+	if( kind == RC_KIND_SKY )
+	{
+		c->base = sky_color;
+		return;
+	}
+
+	float sdivz = sf->d_sdivzorigin + dv * sf->d_sdivzstepv + du * sf->d_sdivzstepu;
+	float tdivz = sf->d_tdivzorigin + dv * sf->d_tdivzstepv + du * sf->d_tdivzstepu;
+	float fpx = (float)px;
+	float sdivzstep = sf->d_sdivzstepu * fpx, tdivzstep = sf->d_tdivzstepu * fpx, zistep = sf->d_zistepu * fpx;
+	int32_t nchunks = rc_span_nchunks( kind, count );
+
+	/* s/t of the span's first pixel: D_DrawSpans16 never reloads s from snext, it keeps stepping
+	 * (s += sstep eight times, sstep = (snext - s) >> 3), so every later chunk start is congruent to
+	 * s0 modulo 8: s_j = snext_(j-1) - ((snext_(j-1) - s0) & 7).  Turbulent8 does reload (r_turb_s = snext). */
+	float z = (float)0x10000 / zi;
+	int32_t s0 = rc_clamp_st( rc_f2i( sdivz * z ) + sf->sadjust, sf->bbextents, 0 );
+	int32_t t0 = rc_clamp_st( rc_f2i( tdivz * z ) + sf->tadjust, sf->bbextentt, 0 );
+	int32_t s = s0, t = t0;
+	if( j )
+	{
+		for( int32_t i = 0; i < j; i++ )
+		{
+			sdivz += sdivzstep; tdivz += tdivzstep; zi += zistep;
+		}
+		z = (float)0x10000 / zi;
+		s = rc_clamp_st( rc_f2i( sdivz * z ) + sf->sadjust, sf->bbextents, px );
+		t = rc_clamp_st( rc_f2i( tdivz * z ) + sf->tadjust, sf->bbextentt, px );
+		if( kind != RC_KIND_TURB )
+		{
+			s -= ( s - s0 ) & 7;
+			t -= ( t - t0 ) & 7;
+		}
+	}
+
+	int32_t spancount = count - j * px;
+	if( j < nchunks - 1 )
+	{
+		sdivz += sdivzstep; tdivz += tdivzstep; zi += zistep;
+		z = (float)0x10000 / zi;
+		int32_t snext = rc_clamp_st( rc_f2i( sdivz * z ) + sf->sadjust, sf->bbextents, px );
+		int32_t tnext = rc_clamp_st( rc_f2i( tdivz * z ) + sf->tadjust, sf->bbextentt, px );
+		int sh = kind == RC_KIND_TURB ? 4 : 3;
+		c->sstep = ( snext - s ) >> sh;
+		c->tstep = ( tnext - t ) >> sh;
+	}
+	else if( spancount > 1 )
+	{
+		float spancountminus1 = (float)( spancount - 1 );
+		sdivz += sf->d_sdivzstepu * spancountminus1;
+		tdivz += sf->d_tdivzstepu * spancountminus1;
+		zi += sf->d_zistepu * spancountminus1;
+		z = (float)0x10000 / zi;
+		int32_t snext = rc_clamp_st( rc_f2i( sdivz * z ) + sf->sadjust, sf->bbextents, px );
+		int32_t tnext = rc_clamp_st( rc_f2i( tdivz * z ) + sf->tadjust, sf->bbextentt, px );
+		c->sstep = ( snext - s ) / ( spancount - 1 );
+		c->tstep = ( tnext - t ) / ( spancount - 1 );
+	}
+	if( kind == RC_KIND_TURB )
+	{
+		s &= ( RC_CYCLE << 16 ) - 1;
+		t &= ( RC_CYCLE << 16 ) - 1;
+	}
+	c->s = s; c->t = t;
+}
+
+/* texel index of pixel i (0-based inside the chunk) - "span texel indices must be integer-exact" */
+RC_HD int32_t rc_pixel_texel( const rc_chunk_t *c, int32_t i, const int32_t *turb )
+{
+	int32_t s = (int32_t)((uint32_t)c->s + (uint32_t)i * (uint32_t)c->sstep );
+	int32_t t = (int32_t)((uint32_t)c->t + (uint32_t)i * (uint32_t)c->tstep );
+	if( c->kind == RC_KIND_TURB )
+	{
+		int32_t sturb = (( s + turb[( t >> 16 ) & ( RC_CYCLE - 1 )] ) >> 16 ) & 63;
+		int32_t tturb = (( t + turb[( s >> 16 ) & ( RC_CYCLE - 1 )] ) >> 16 ) & 63;
+		return c->base + ( tturb << 6 ) + sturb;
+	}
+	return c->base + ( s >> 16 ) + ( t >> 16 ) * c->width;
+}
+
+RC_HD int16_t rc_pixel_z( const rc_chunk_t *c, int32_t i )
+{
+	return (int16_t)((int32_t)((uint32_t)c->izi + (uint32_t)i * (uint32_t)c->izistep ) >> 16 );
+}
+
+/* ------------------------------------------------------------------------------------------ */
+/* A7/A8: light map blend and surface cache block (ref/soft/r_surf.c:174-229,291-757)            */
+
+/* R_BuildLightMap for luxel i of a face: sum of (r+g+b) * style value, gamma, quantise to bits 8..12 */
+RC_HD uint32_t rc_blocklight( const rc_scene_t *sc, const rc_surface_t *sf, const int32_t *stylevalue, int32_t size, int32_t i )
+{
+	uint32_t bl = 0;
+	if( sf->lightofs >= 0 )
+	{
+		for( int map = 0; map < RC_MAXLIGHTMAPS; map++ )
+		{
+			if( sf->styles[map] >= 255 )
+				break;
+			uint32_t scale = (uint32_t)stylevalue[sf->styles[map]];
+			const uint8_t *lm = sc->lightdata + 3 * ((size_t)sf->lightofs + (size_t)map * size + i );
+			bl += ((uint32_t)lm[0] + lm[1] + lm[2] ) * scale;
+		}
+	}
+	int32_t t;
+	if( bl < 65280 )
+	{
+		uint32_t b = bl >> 6;
+		t = (int32_t)(( b >= 1024 ? 0u : (uint32_t)sc->lightgamma[b] ) << 6 );
+	}
+	else t = (int32_t)bl;
+	t = t >= 0 ? ( t < 65535 * 3 ? t : 65535 * 3 ) : 0; /* bound( 0, t, 65535 * 3 ) */
+	t = t / 2048 / 3;
+	return (uint32_t)( t << 8 );
+}
+
+/*
+ * One texel (x, y) of the cache block of (face, mip): R_DrawSurface + R_DrawSurfaceBlock8_mipN in
+ * closed form.  blocklights = the face's luxel grid (lightwidth per row) from rc_blocklight.
+ * All light arithmetic is uint32 with the reference's wraparound and unsigned shifts.
+ */
+RC_HD uint16_t rc_cache_texel( const rc_scene_t *sc, const rc_surface_t *sf, const rc_texture_t *tex, int32_t mip,
+	const uint32_t *blocklights, int32_t lightwidth, int32_t x, int32_t y )
+{
+	int32_t k = 4 - mip, bs = 16 >> mip;
+	int32_t bu = x >> k, b = x & ( bs - 1 ), bv = y >> k, i = y & ( bs - 1 );
+
+	const uint32_t *lp = blocklights + bv * lightwidth + bu;
+	uint32_t ll = lp[0], lr = lp[1];
+	uint32_t lls = ( lp[lightwidth] - ll ) >> k, lrs = ( lp[lightwidth + 1] - lr ) >> k;
+	ll += (uint32_t)i * lls; lr += (uint32_t)i * lrs;
+	uint32_t step = ( ll - lr ) >> k;
+	uint32_t light = lr + (uint32_t)( bs - 1 - b ) * step;
+
+	/* source texel: column offset advances per block column and snaps to 0 past the texture width,
+	 * row offset advances per block row and steps back by the texture height (r_surf.c:411-426,586-600) */
+	int32_t smax = tex->width >> mip, tmax = tex->height >> mip;
+	if( smax < 1 ) smax = 1;
+	if( tmax < 1 ) tmax = 1;
+	int32_t soffset = ((( (int32_t)sf->lightmapmins[0] ) >> mip ) + ( smax << 16 )) % smax;
+	for( int32_t q = 0; q < bu; q++ )
+	{
+		soffset += bs;
+		if( soffset >= smax ) soffset = 0;
+	}
+	int32_t rowofs = (((( (int32_t)sf->lightmapmins[1] ) >> mip ) + ( tmax << 16 )) % tmax ) * smax;
+	int32_t total = tmax * smax;
+	for( int32_t q = 0; q < bv; q++ )
+	{
+		rowofs += bs * smax;
+		if( rowofs + soffset >= total ) rowofs -= total; /* psource >= r_sourcemax */
+	}
+	int32_t idx = rowofs + i * smax + soffset + b;
+	/* the reference reads past the mip when a texture is not a multiple of the block size; stay inside the arena */
+	int32_t lim = tex->width * tex->height * 2;
+	if( idx < 0 ) idx = 0;
+	if( idx >= lim ) idx = lim - 1;
+	uint16_t pix = sc->texels[tex->ofs[mip] + idx];
+	uint16_t out = (uint16_t)( sc->colormap[( pix >> 3 ) | (( light & 0x1f00 ) << 5 )] | ( pix & 7 ));
+	if( mip == 0 && pix == RC_TRANSPARENT_COLOR )
+		out = RC_TRANSPARENT_COLOR;
+	return out;
+}
+
+#endif /* RC_CORE_H */

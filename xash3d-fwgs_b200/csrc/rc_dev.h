@@ -1,0 +1,57 @@
+/*
+ * rc_dev.h - the thin C layer between the plugin's C host code (rc_host.c) and the sm_100a kernels
+ * (rc_device.cu).  Plain pointers and sizes only.  Every function returns 0 on success, non-zero on a
+ * CUDA error (text via rc_dev_last_error); there is no CPU implementation behind these entry points in
+ * libref_cuda.so - without a CUDA device rc_dev_init fails and R_Init reports it.
+ */
+#ifndef RC_DEV_H
+#define RC_DEV_H
+
+#include <stddef.h>
+#include "rc_shared.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+int rc_dev_init( int device );
+void rc_dev_shutdown( void );
+const char *rc_dev_last_error( void );
+const char *rc_dev_name( void );
+
+/* static tables: colormap[32*8192] u16, lightgamma[1024] u16, sintable[1280] i32 */
+int rc_dev_upload_luts( const uint16_t *colormap, const uint16_t *lightgamma, const int32_t *sintable );
+/* texture table + texel arena (pixel_t), replaces the previous one */
+int rc_dev_upload_textures( const rc_texture_t *tex, int ntex, const uint16_t *texels, size_t ntexels );
+/* world arrays: sc holds HOST pointers and counts; cache_texels = size of the surface cache arena */
+int rc_dev_upload_scene( const rc_scene_t *sc, size_t cache_texels );
+/* texture number per surface after R_TextureAnimation (only changes when animated textures flip) */
+int rc_dev_update_surface_texnums( const int32_t *texnum, int n );
+/* g_lightstylevalue[256] for the next batch (ref/common/ref_light.c:30-87) */
+int rc_dev_set_lightstyles( const int32_t *values );
+/* drop every cached block (D_FlushCaches, ref/soft/r_surf.c:810) */
+int rc_dev_flush_cache( void );
+
+/*
+ * Render nviews views of width x height (each view owns one width x height pixel_t buffer and z buffer).
+ * color_out / z_out: HOST destinations [nviews][height][width] or NULL to leave results in HBM.
+ * clear: non-zero -> framebuffers start as zeros (the reference never clears; harnesses zero both sides).
+ */
+int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, int clear, uint16_t *color_out, int16_t *z_out );
+
+/* re-run the device stages of the last rc_dev_render batch (inputs resident in HBM) 'iters' times and
+ * report CUDA-event milliseconds: total and per stage (vis+walk, faces, cache, scan) */
+int rc_dev_bench_resident( int iters, int rebuild_cache, float *ms_total, float *ms_stage /* [4] */ );
+
+/* probes for the parity tests */
+int rc_dev_read_cache_block( int surf, int mip, uint16_t *out, int maxtexels, int *width, int *height, int *valid );
+int rc_dev_read_counters( uint64_t *out, int n );
+int rc_dev_read_view_surfs( int view, rc_surf_t *out, int max, int *n );
+int rc_dev_read_view_edges( int view, rc_edge_t *out, int max, int *n );
+/* launch counter: kernels of ours launched since init */
+uint64_t rc_dev_launch_count( void );
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,1132 @@
+/*
+ * rc_host.c - ref/cuda: a renderer plugin for Xash3D FWGS that exports the GetRefAPI /
+ * ref_interface_t surface of engine/ref_api.h (:527-661) and renders batched camera views of BSP30
+ * worlds with sm_100a CUDA kernels (rc_device.cu).  Drop-in for ref/soft (`-ref cuda`).
+ *
+ * This file is the C host side: the 78-slot function table, the texture table (pixel_t encoding of
+ * ref/soft/r_image.c:214-277 restated), the blend LUT builder (r_glblit.c:411-470), the flattening of
+ * the engine's model_t into device arrays at R_NewMap, the per-view constants of
+ * R_SetupFrustum/R_SetupFrameQ/R_ViewChanged (r_main.c:387, r_misc.c:101-322), light styles
+ * (ref/common/ref_light.c:30-87) and the view queue.  All pixels are produced on the GPU; there is no
+ * CPU rasteriser in this library.
+ */
+#define REF_DLL 1
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <strings.h>
+
+#include "build.h"
+#include "port.h"
+#include "xash3d_types.h"
+#include "const.h"
+#include "cvardef.h"
+#include "com_model.h"
+#include "cl_entity.h"
+#include "ref_api.h"
+#include "ref_params.h"
+#include "enginefeatures.h"
+#include "com_strings.h"
+#include "lightstyle.h"
+#include "xash3d_mathlib.h"
+
+#include "rc_dev.h"
+#include "ref_cuda.h"
+
+#define RC_MAX_TEXTURES 8192
+#define RC_MAX_QUEUED_VIEWS 16384
+#define LM_SAMPLE_SIZE 16
+
+DEFINE_ENGINE_SHARED_CVAR_LIST()
+
+ref_api_t      gEngfuncs;
+ref_globals_t *gpGlobals;
+static ref_client_t *gp_cl;
+static ref_host_t   *gp_host;
+
+static CVAR_DEFINE_AUTO( sw_clearcolor, "48999", 0, "screen clear color" );
+static CVAR_DEFINE_AUTO( sw_mipcap, "0", FCVAR_GLCONFIG, "" );
+static CVAR_DEFINE_AUTO( sw_mipscale, "1", FCVAR_GLCONFIG, "nothing" );
+static CVAR_DEFINE_AUTO( sw_noalphabrushes, "0", FCVAR_GLCONFIG, "" );
+static CVAR_DEFINE_AUTO( cu_device, "0", FCVAR_GLCONFIG, "CUDA device ordinal used by ref_cuda" );
+static CVAR_DEFINE_AUTO( r_novis, "0", 0, "" );
+
+/* ---------------------------------------------------------------------------------------------- */
+/* texture table (image_t of ref/soft/r_local.h:287-312, host mirror; texels are uploaded as one arena) */
+
+typedef struct
+{
+	char      name[256];
+	int       width, height, srcWidth, srcHeight;
+	uint      flags;
+	uint16_t *pixels[4];
+	uint16_t *alpha_pixels;
+} rc_image_t;
+
+static struct
+{
+	qboolean     initialized;
+	poolhandle_t pool;
+	rc_image_t   images[RC_MAX_TEXTURES];
+	int          numImages;
+	qboolean     textures_dirty;
+
+	uint16_t     colormap[32 * 8192];
+	int32_t      sintable[1280];
+	const uint16_t *lightgamma; /* engine table */
+
+	int          lightstylevalue[MAX_LIGHTSTYLES];
+
+	/* world */
+	model_t     *world;
+	qboolean     scene_valid;
+	int32_t     *surf_texnum;
+	int          maxdepth;
+
+	/* view queue between R_BeginFrame and R_EndFrame */
+	rc_view_t   *views;
+	int          nviews, maxviews;
+	uint16_t    *framebuf; /* host copy of the last flushed batch's first view (blit source) */
+	int16_t     *zbuf;
+	int          fb_w, fb_h;
+
+	void        *swbuffer_info_valid;
+	uint         sw_stride, sw_bpp, sw_r, sw_g, sw_b;
+	char         error[512];
+} rc;
+
+static void rc_strncpy( char *dst, const char *src, size_t n ) { strncpy( dst, src, n - 1 ); dst[n - 1] = 0; }
+
+static void rc_error( const char *fmt, ... )
+{
+	va_list ap;
+	va_start( ap, fmt );
+	vsnprintf( rc.error, sizeof( rc.error ), fmt, ap );
+	va_end( ap );
+	gEngfuncs.Con_Printf( S_ERROR "ref_cuda: %s\n", rc.error );
+}
+
+#define RC_CHECK_DEV( call ) do { if(( call ) != 0 ) gEngfuncs.Host_Error( "ref_cuda: %s failed: %s\n", #call, rc_dev_last_error()); } while( 0 )
+
+static void *rc_malloc( size_t n ) { return gEngfuncs._Mem_Alloc( rc.pool, n, true, __FILE__, __LINE__ ); }
+static void rc_free( void *p ) { if( p ) gEngfuncs._Mem_Free( p, __FILE__, __LINE__ ); }
+
+/* pixel_t code of an RGB triple already reduced to 5/6/5 bits: major RGB332 << 8 | minor GBRGBRGB
+ * (ref/soft/r_image.c:261-271, r_glblit.c:463-468) */
+static uint16_t rc_encode565( uint r, uint g, uint b )
+{
+	uint major = ((( r >> 2 ) & 7 ) << 5 ) | ((( g >> 3 ) & 7 ) << 2 ) | (( b >> 3 ) & 3 );
+	uint minor = ((( r >> 1 ) & 1 ) << 5 ) | (( r & 1 ) << 2 )
+		| ((( g >> 2 ) & 1 ) << 7 ) | ((( g >> 1 ) & 1 ) << 4 ) | (( g & 1 ) << 1 )
+		| ((( b >> 2 ) & 1 ) << 6 ) | ((( b >> 1 ) & 1 ) << 3 ) | ( b & 1 );
+	return (uint16_t)( major << 8 | ( minor & 0xFF ));
+}
+
+/* the 565 triple a pixel_t code stands for (inverse of the above, r_glblit.c:447-452) */
+static void rc_decode565( uint color, uint *r, uint *g, uint *b )
+{
+	uint m = color >> 8, j = color & 0xFF;
+	*r = ((( m >> 5 ) << 2 ) & 31 ) | ((( j >> 5 ) & 1 ) << 1 ) | (( j >> 2 ) & 1 );
+	*g = ((( m >> 2 ) << 3 ) & 63 ) | ((( j >> 7 ) & 1 ) << 2 ) | ((( j >> 4 ) & 1 ) << 1 ) | (( j >> 1 ) & 1 );
+	*b = (( m << 3 ) & 31 ) | ((( j >> 6 ) & 1 ) << 2 ) | ((( j >> 3 ) & 1 ) << 1 ) | ( j & 1 );
+}
+
+/* vid.colormap of R_BuildBlendMaps (r_glblit.c:440-470): 32 light levels x 8192 colour codes (pixel >> 3) */
+static void rc_build_colormap( void )
+{
+	for( uint i = 0; i < 8192; i++ )
+	{
+		uint r1, g1, b1;
+		rc_decode565( i << 3, &r1, &g1, &b1 );
+		for( uint j = 0; j < 32; j++ )
+			rc.colormap[( j << 13 ) | i] = rc_encode565( r1 * j / 32, g1 * j / 32, b1 * j / 32 );
+	}
+}
+
+static rc_image_t *rc_find_image( const char *name )
+{
+	for( int i = 0; i < rc.numImages; i++ )
+		if( rc.images[i].name[0] && !strcasecmp( rc.images[i].name, name ))
+			return &rc.images[i];
+	return NULL;
+}
+
+static rc_image_t *rc_alloc_image( const char *name, uint flags )
+{
+	int i;
+	for( i = 0; i < rc.numImages; i++ )
+		if( !rc.images[i].name[0] )
+			break;
+	if( i == rc.numImages )
+	{
+		if( rc.numImages == RC_MAX_TEXTURES )
+			gEngfuncs.Host_Error( "%s: MAX_TEXTURES limit exceeds\n", __func__ );
+		rc.numImages++;
+	}
+	rc_image_t *tex = &rc.images[i];
+	memset( tex, 0, sizeof( *tex ));
+	rc_strncpy( tex->name, name, sizeof( tex->name ));
+	tex->flags = flags;
+	return tex;
+}
+
+static void rc_delete_image( rc_image_t *tex )
+{
+	for( int i = 0; i < 4; i++ ) rc_free( tex->pixels[i] );
+	rc_free( tex->alpha_pixels );
+	memset( tex, 0, sizeof( *tex ));
+	rc.textures_dirty = true;
+}
+
+/* box filter in place, quartering the image (the colour path of GL_BuildMipMap, r_image.c:125-207) */
+static void rc_build_mipmap( byte *in, int srcWidth, int srcHeight )
+{
+	byte *out = in;
+	int instride = srcWidth * 4;
+	int mipWidth = Q_max( 1, srcWidth >> 1 ), mipHeight = Q_max( 1, srcHeight >> 1 );
+
+	for( int y = 0; y < mipHeight; y++, in += instride * 2 )
+	{
+		byte *next = ((( y << 1 ) + 1 ) < srcHeight ) ? ( in + instride ) : in;
+		for( int x = 0, row = 0; x < mipWidth; x++, row += 8, out += 4 )
+		{
+			if((( x << 1 ) + 1 ) < srcWidth )
+			{
+				for( int c = 0; c < 4; c++ )
+					out[c] = ( in[row + c] + in[row + 4 + c] + next[row + c] + next[row + 4 + c] ) >> 2;
+			}
+			else
+			{
+				for( int c = 0; c < 4; c++ )
+					out[c] = ( in[row + c] + next[row + c] ) >> 1;
+			}
+		}
+	}
+}
+
+/* GL_UploadTexture (r_image.c:214-283): RGBA8 -> pixel_t for 4 mips, alpha plane, colour key.
+ * Like the reference it filters the caller's RGBA buffer in place. */
+static qboolean rc_upload_image( rc_image_t *tex, rgbdata_t *pic )
+{
+	tex->srcWidth = tex->width = Q_max( 1, pic->width );
+	tex->srcHeight = tex->height = Q_max( 1, pic->height );
+	if( pic->flags & IMAGE_HAS_ALPHA )
+		tex->flags |= TF_HAS_ALPHA;
+	if( !pic->buffer )
+		return true;
+	if( pic->type != PF_RGBA_32 )
+	{
+		rc_error( "texture %s: unsupported pixel format %d", tex->name, pic->type );
+		return false;
+	}
+
+	byte *data = pic->buffer;
+	for( uint j = 0; j < 4; j++ )
+	{
+		uint width = Q_max( 1, ( tex->width >> j )), height = Q_max( 1, ( tex->height >> j ));
+
+		rc_free( tex->pixels[j] );
+		tex->pixels[j] = rc_malloc( width * height * sizeof( uint16_t ));
+		if( j == 0 && ( tex->flags & TF_HAS_ALPHA ))
+		{
+			rc_free( tex->alpha_pixels );
+			tex->alpha_pixels = rc_malloc( width * height * sizeof( uint16_t ));
+		}
+		for( uint i = 0; i < height * width; i++ )
+		{
+			uint r = data[i * 4 + 0] * 32 / 256, g = data[i * 4 + 1] * 64 / 256, b = data[i * 4 + 2] * 32 / 256;
+			tex->pixels[j][i] = rc_encode565( r, g, b );
+			if( j == 0 && tex->alpha_pixels )
+			{
+				uint alpha = ( data[i * 4 + 3] * 8 / 256 ) << ( 16 - 3 );
+				tex->alpha_pixels[i] = ( tex->pixels[j][i] >> 3 ) | alpha;
+				if( !sw_noalphabrushes.value && data[i * 4 + 3] < 128 && FBitSet( pic->flags, IMAGE_ONEBIT_ALPHA ))
+					tex->pixels[j][i] = RC_TRANSPARENT_COLOR;
+			}
+		}
+		rc_build_mipmap( data, width, height );
+	}
+	rc.textures_dirty = true;
+	return true;
+}
+
+static int GL_LoadTextureFromBuffer( const char *name, rgbdata_t *pic, texFlags_t flags, qboolean update )
+{
+	if( ( !name || !name[0] ) || strlen( name ) >= sizeof( rc.images->name ))
+		return 0;
+
+	rc_image_t *tex = rc_find_image( name );
+	if( tex && !update )
+		return tex - rc.images;
+	if( !pic )
+		return 0;
+	if( update )
+	{
+		if( !tex )
+			gEngfuncs.Host_Error( "%s: couldn't find texture %s for update\n", __func__, name );
+		SetBits( tex->flags, flags );
+	}
+	else tex = rc_alloc_image( name, flags );
+
+	if( !rc_upload_image( tex, pic ))
+	{
+		memset( tex, 0, sizeof( *tex ));
+		return 0;
+	}
+	return tex - rc.images;
+}
+
+static int GL_LoadTexture( const char *name, const byte *buf, size_t size, int flags )
+{
+	if( ( !name || !name[0] ) || strlen( name ) >= sizeof( rc.images->name ))
+		return 0;
+
+	rc_image_t *tex = rc_find_image( name );
+	if( tex )
+		return tex - rc.images;
+
+	uint picFlags = 0;
+	if( FBitSet( flags, TF_NOFLIP_TGA )) SetBits( picFlags, IL_DONTFLIP_TGA );
+	if( FBitSet( flags, TF_KEEP_SOURCE ) && !FBitSet( flags, TF_EXPAND_SOURCE )) SetBits( picFlags, IL_KEEP_8BIT );
+	gEngfuncs.Image_SetForceFlags( picFlags );
+
+	rgbdata_t *pic = gEngfuncs.FS_LoadImage( name, buf, size );
+	if( !pic )
+		return 0;
+
+	tex = rc_alloc_image( name, flags );
+	if( !rc_upload_image( tex, pic ))
+	{
+		memset( tex, 0, sizeof( *tex ));
+		gEngfuncs.FS_FreeImage( pic );
+		return 0;
+	}
+	gEngfuncs.FS_FreeImage( pic );
+	return tex - rc.images;
+}
+
+static int GL_CreateTexture( const char *name, int width, int height, const void *buffer, texFlags_t flags )
+{
+	rgbdata_t r_empty;
+	memset( &r_empty, 0, sizeof( r_empty ));
+	r_empty.width = width;
+	r_empty.height = height;
+	r_empty.type = PF_RGBA_32;
+	r_empty.size = width * height * 4;
+	r_empty.flags = IMAGE_HAS_COLOR | ( FBitSet( flags, TF_HAS_ALPHA ) ? IMAGE_HAS_ALPHA : 0 );
+	if( FBitSet( flags, TF_CUBEMAP ))
+		return 0;
+
+	/* the upload filters its source in place (as the reference does): work on a copy of caller memory */
+	byte *copy = NULL;
+	if( buffer )
+	{
+		copy = rc_malloc( r_empty.size );
+		memcpy( copy, buffer, r_empty.size );
+	}
+	r_empty.buffer = copy;
+	int texnum = GL_LoadTextureFromBuffer( name, &r_empty, flags, false );
+	rc_free( copy );
+	return texnum;
+}
+
+static int GL_FindTexture( const char *name )
+{
+	rc_image_t *tex = name ? rc_find_image( name ) : NULL;
+	return tex ? tex - rc.images : 0;
+}
+
+static const char *GL_TextureName( unsigned int texnum )
+{
+	return texnum < RC_MAX_TEXTURES ? rc.images[texnum].name : "";
+}
+
+static const byte *GL_TextureData( unsigned int texnum ) { (void)texnum; return NULL; }
+
+static void GL_FreeTexture( unsigned int texnum )
+{
+	if( texnum == 0 || texnum >= RC_MAX_TEXTURES || !rc.images[texnum].name[0] )
+		return;
+	rc_delete_image( &rc.images[texnum] );
+}
+
+/* pack every live texture into one pixel_t arena and hand it to the device */
+static void rc_sync_textures( void )
+{
+	if( !rc.textures_dirty )
+		return;
+
+	size_t total = 0;
+	for( int i = 0; i < rc.numImages; i++ )
+	{
+		rc_image_t *t = &rc.images[i];
+		if( !t->pixels[0] ) continue;
+		for( int j = 0; j < 4; j++ )
+			total += (size_t)Q_max( 1, t->width >> j ) * Q_max( 1, t->height >> j );
+		if( t->alpha_pixels ) total += (size_t)t->width * t->height;
+	}
+	rc_texture_t *tab = rc_malloc( sizeof( rc_texture_t ) * Q_max( 1, rc.numImages ));
+	uint16_t *arena = rc_malloc(( total + 64 ) * sizeof( uint16_t ));
+	size_t o = 0;
+	for( int i = 0; i < rc.numImages; i++ )
+	{
+		rc_image_t *t = &rc.images[i];
+		rc_texture_t *d = &tab[i];
+		d->width = t->width; d->height = t->height; d->flags = t->flags; d->alpha_ofs = -1;
+		for( int j = 0; j < 4; j++ ) d->ofs[j] = 0;
+		if( !t->pixels[0] ) continue;
+		for( int j = 0; j < 4; j++ )
+		{
+			size_t n = (size_t)Q_max( 1, t->width >> j ) * Q_max( 1, t->height >> j );
+			d->ofs[j] = (int32_t)o;
+			memcpy( arena + o, t->pixels[j], n * sizeof( uint16_t ));
+			o += n;
+		}
+		if( t->alpha_pixels )
+		{
+			size_t n = (size_t)t->width * t->height;
+			d->alpha_ofs = (int32_t)o;
+			memcpy( arena + o, t->alpha_pixels, n * sizeof( uint16_t ));
+			o += n;
+		}
+	}
+	RC_CHECK_DEV( rc_dev_upload_textures( tab, rc.numImages, arena, total + 64 ));
+	rc_free( tab );
+	rc_free( arena );
+	rc.textures_dirty = false;
+}
+
+/* ---------------------------------------------------------------------------------------------- */
+/* world flattening: engine model_t (common/com_model.h) -> rc_scene_t arrays                       */
+
+static int rc_node_ref( const model_t *mod, const mnode_t *n )
+{
+	if( n->contents < 0 )
+		return -1 - (int)((const mleaf_t *)n - mod->leafs );
+	return (int)( n - mod->nodes );
+}
+
+static int rc_tree_depth( const model_t *mod, const mnode_t *n, int d )
+{
+	if( n->contents < 0 )
+		return d;
+	int a = rc_tree_depth( mod, node_child( n, 0, mod ), d + 1 );
+	int b = rc_tree_depth( mod, node_child( n, 1, mod ), d + 1 );
+	return a > b ? a : b;
+}
+
+/* R_TextureAnimation (ref/soft/r_surf.c:239-284) for the world entity (curstate.frame == 0) */
+static uint16_t rc_rtable[MOD_FRAMES][MOD_FRAMES];
+
+static int rc_texture_animation( const msurface_t *s )
+{
+	texture_t *base = s->texinfo->texture;
+	int reletive;
+
+	if( !base->anim_total )
+		return base->gl_texturenum;
+
+	if( base->name[0] == '-' )
+	{
+		int tx = (int)(( s->texturemins[0] + ( base->width << 16 )) / base->width ) % MOD_FRAMES;
+		int ty = (int)(( s->texturemins[1] + ( base->height << 16 )) / base->height ) % MOD_FRAMES;
+		reletive = rc_rtable[tx][ty] % base->anim_total;
+	}
+	else
+	{
+		int speed = FBitSet( rc.images[base->gl_texturenum].flags, TF_QUAKEPAL ) ? 10 : 20;
+		reletive = (int)( gp_cl->time * speed ) % base->anim_total;
+	}
+
+	int count = 0;
+	while( base->anim_min > reletive || base->anim_max <= reletive )
+	{
+		base = base->anim_next;
+		if( !base || ++count > MOD_FRAMES )
+			return s->texinfo->texture->gl_texturenum;
+	}
+	return base->gl_texturenum;
+}
+
+static void rc_resolve_texnums( qboolean force )
+{
+	model_t *w = rc.world;
+	qboolean changed = force;
+	for( int i = 0; i < w->numsurfaces; i++ )
+	{
+		int t = rc_texture_animation( &w->surfaces[i] );
+		if( t != rc.surf_texnum[i] ) { rc.surf_texnum[i] = t; changed = true; }
+	}
+	if( changed && !force )
+		RC_CHECK_DEV( rc_dev_update_surface_texnums( rc.surf_texnum, w->numsurfaces ));
+}
+
+static void R_NewMap( void )
+{
+	model_t *w = gp_cl->models[1];
+	rc.world = w;
+	rc.scene_valid = false;
+	if( !w )
+		return;
+	if( FBitSet( w->flags, MODEL_QBSP2 ))
+	{
+		gEngfuncs.Host_Error( "Sorry, ref_cuda can't load maps in BSP2 format.\n" );
+		return;
+	}
+
+	int numleafs = w->numleafs + 1; /* model_t.numleafs excludes the shared solid leaf 0 */
+	rc_scene_t sc;
+	memset( &sc, 0, sizeof( sc ));
+	sc.numplanes = w->numplanes; sc.numnodes = w->numnodes; sc.numleafs = numleafs;
+	sc.numsurfaces = w->numsurfaces; sc.nummarks = w->nummarksurfaces; sc.numsurfedges = w->numsurfedges;
+	sc.numedges = w->numedges; sc.numverts = w->numvertexes;
+	sc.numclusters = w->numleafs;
+	sc.visbytes = ( w->numleafs + 7 ) >> 3;
+	sc.headnode = 0;
+
+	rc_plane_t *planes = rc_malloc( sizeof( rc_plane_t ) * Q_max( 1, w->numplanes ));
+	for( int i = 0; i < w->numplanes; i++ )
+	{
+		VectorCopy( w->planes[i].normal, planes[i].normal );
+		planes[i].dist = w->planes[i].dist;
+		planes[i].type = w->planes[i].type;
+	}
+
+	rc_node_t *nodes = rc_malloc( sizeof( rc_node_t ) * Q_max( 1, w->numnodes ));
+	for( int i = 0; i < w->numnodes; i++ )
+	{
+		const mnode_t *n = &w->nodes[i];
+		nodes[i].plane = (int)( n->plane - w->planes );
+		nodes[i].child[0] = rc_node_ref( w, node_child( n, 0, w ));
+		nodes[i].child[1] = rc_node_ref( w, node_child( n, 1, w ));
+		nodes[i].parent = n->parent ? (int)( n->parent - w->nodes ) : -1;
+		nodes[i].firstsurface = node_firstsurface( n, w );
+		nodes[i].numsurfaces = node_numsurfaces( n, w );
+		memcpy( nodes[i].minmaxs, n->minmaxs, sizeof( n->minmaxs ));
+	}
+
+	/* the PVS rows live inside model_t.visdata; a leaf's row is addressed by offset */
+	size_t vislen = 0;
+	rc_leaf_t *leafs = rc_malloc( sizeof( rc_leaf_t ) * numleafs );
+	for( int i = 0; i < numleafs; i++ )
+	{
+		const mleaf_t *l = &w->leafs[i];
+		leafs[i].contents = l->contents;
+		leafs[i].cluster = l->cluster;
+		leafs[i].parent = l->parent ? (int)( l->parent - w->nodes ) : -1;
+		leafs[i].firstmark = l->firstmarksurface ? (int)( l->firstmarksurface - w->marksurfaces ) : 0;
+		leafs[i].nummark = l->nummarksurfaces;
+		leafs[i].visofs = ( l->compressed_vis && w->visdata ) ? (int)( l->compressed_vis - w->visdata ) : -1;
+		memcpy( leafs[i].minmaxs, l->minmaxs, sizeof( l->minmaxs ));
+		if( leafs[i].visofs >= 0 )
+		{
+			/* walk the row to find where the lump ends (model_t does not keep the lump size) */
+			const byte *in = l->compressed_vis;
+			int d = 0;
+			while( d < sc.visbytes )
+			{
+				if( *in ) { d++; in++; }
+				else { d += in[1]; in += 2; }
+			}
+			size_t end = (size_t)( in - w->visdata );
+			if( end > vislen ) vislen = end;
+		}
+	}
+	sc.visdata_len = w->visdata ? (int)Q_max( vislen, 1 ) : 0;
+
+	int32_t *marks = rc_malloc( sizeof( int32_t ) * Q_max( 1, w->nummarksurfaces ));
+	for( int i = 0; i < w->nummarksurfaces; i++ )
+		marks[i] = (int)( w->marksurfaces[i] - w->surfaces );
+
+	uint16_t *edges = rc_malloc( sizeof( uint16_t ) * 2 * Q_max( 1, w->numedges ));
+	for( int i = 0; i < w->numedges; i++ )
+	{
+		edges[2 * i] = w->edges16[i].v[0];
+		edges[2 * i + 1] = w->edges16[i].v[1];
+	}
+
+	/* lighting: byte length = end of the furthest sample block */
+	size_t lightlen = 0;
+	rc_free( rc.surf_texnum );
+	rc.surf_texnum = rc_malloc( sizeof( int32_t ) * Q_max( 1, w->numsurfaces ));
+	rc_surface_t *surfs = rc_malloc( sizeof( rc_surface_t ) * Q_max( 1, w->numsurfaces ));
+	size_t cache_texels = 0;
+	for( int i = 0; i < w->numsurfaces; i++ )
+	{
+		const msurface_t *s = &w->surfaces[i];
+		const mextrasurf_t *info = s->info;
+		rc_surface_t *d = &surfs[i];
+		d->plane = (int)( s->plane - w->planes );
+		d->flags = s->flags;
+		d->firstedge = s->firstedge;
+		d->numedges = s->numedges;
+		d->texnum = rc.surf_texnum[i] = rc_texture_animation( s );
+		d->sample_size = gEngfuncs.Mod_SampleSizeForFace( s );
+		d->texflags = s->texinfo->flags;
+		for( int j = 0; j < 4; j++ ) d->styles[j] = s->styles[j];
+		for( int j = 0; j < 2; j++ )
+		{
+			d->texturemins[j] = s->texturemins[j];
+			d->extents[j] = s->extents[j];
+			d->lightmapmins[j] = info->lightmapmins[j];
+			d->lightextents[j] = info->lightextents[j];
+			for( int k = 0; k < 4; k++ ) d->lmvecs[j][k] = info->lmvecs[j][k];
+		}
+		d->lightofs = -1;
+		if( s->samples && w->lightdata )
+		{
+			d->lightofs = (int)( s->samples - w->lightdata );
+			int smax = info->lightextents[0] / d->sample_size + 1, tmax = info->lightextents[1] / d->sample_size + 1;
+			int nstyles = 0;
+			while( nstyles < 4 && s->styles[nstyles] != 255 ) nstyles++;
+			size_t end = ((size_t)d->lightofs + (size_t)smax * tmax * nstyles ) * 3;
+			if( end > lightlen ) lightlen = end;
+		}
+		/* every (face,mip) block gets a fixed home in the cache arena: 180 GB of HBM removes the need for the
+		 * reference's ring allocator and its evictions (D_SCAlloc, ref/soft/r_surf.c:833) */
+		for( int m = 0; m < 4; m++ )
+		{
+			d->cache_ofs[m] = -1;
+			if( FBitSet( s->flags, SURF_DRAWSKY | SURF_DRAWTURB ) || d->sample_size != 16 )
+				continue;
+			int cw = info->lightextents[0] >> m, ch = info->lightextents[1] >> m;
+			if( cw <= 0 || ch <= 0 ) continue;
+			d->cache_ofs[m] = (int32_t)cache_texels;
+			cache_texels += ((size_t)cw * ch + 7 ) & ~(size_t)7;
+		}
+	}
+	sc.lightdata_len = (int)lightlen;
+
+	sc.planes = planes; sc.nodes = nodes; sc.leafs = leafs; sc.surfaces = surfs; sc.marksurfaces = marks;
+	sc.surfedges = w->surfedges; sc.edges = edges; sc.verts = (const float *)w->vertexes;
+	sc.visdata = w->visdata; sc.lightdata = (const uint8_t *)w->lightdata;
+
+	rc.maxdepth = rc_tree_depth( w, w->nodes, 0 );
+	sc.pad0 = rc.maxdepth;
+
+	rc_sync_textures();
+	RC_CHECK_DEV( rc_dev_upload_scene( &sc, cache_texels + 64 ));
+	rc.scene_valid = true;
+
+	rc_free( planes ); rc_free( nodes ); rc_free( leafs ); rc_free( marks ); rc_free( edges ); rc_free( surfs );
+	gEngfuncs.Con_Reportf( "ref_cuda: world %d faces, %d nodes, %d leafs, tree depth %d, surface cache %.1f MB\n",
+		w->numsurfaces, w->numnodes, numleafs, rc.maxdepth, cache_texels * 2.0 / 1048576.0 );
+}
+
+/* ---------------------------------------------------------------------------------------------- */
+/* light styles: CL_RunLightStyles, ref/common/ref_light.c:30-87                                   */
+
+static void CL_RunLightStyles( lightstyle_t *ls )
+{
+	const model_t *world = gp_cl->models[1];
+	float frametime = gp_cl->time - gp_cl->oldtime;
+
+	if( !world )
+		return;
+
+	if( r_fullbright->value || !world->lightdata )
+	{
+		for( int i = 0; i < MAX_LIGHTSTYLES; i++ )
+			rc.lightstylevalue[i] = 256 * 256;
+		return;
+	}
+
+	for( int i = 0; i < MAX_LIGHTSTYLES; i++ )
+	{
+		if( !gp_cl->paused && frametime <= 0.1f )
+			ls[i].time += frametime;
+
+		if( !ls[i].length )
+		{
+			rc.lightstylevalue[i] = 256;
+			continue;
+		}
+		if( ls[i].length == 1 )
+		{
+			rc.lightstylevalue[i] = ls[i].map[0] * 22;
+			continue;
+		}
+
+		int flight = (int)Q_floor( ls[i].time * 10 );
+		if( !ls[i].interp || !cl_lightstyle_lerping->value )
+		{
+			rc.lightstylevalue[i] = ls[i].map[flight % ls[i].length] * 22;
+			continue;
+		}
+
+		int clight = (int)Q_ceil( ls[i].time * 10 );
+		float lerpfrac = ( ls[i].time * 10 ) - flight;
+		float backlerp = 1.0f - lerpfrac;
+		int k = ls[i].map[flight % ls[i].length];
+		float l = (float)( k * 22.0f ) * backlerp;
+		k = ls[i].map[clight % ls[i].length];
+		l += (float)( k * 22.0f ) * lerpfrac;
+		rc.lightstylevalue[i] = (int)l;
+	}
+}
+
+/* ---------------------------------------------------------------------------------------------- */
+/* per-view constants                                                                               */
+
+/*
+ * R_SetupFrustum (ref/soft/r_main.c:387) + R_SetupFrameQ / R_ViewChanged / R_TransformFrustum /
+ * R_SetUpFrustumIndexes (r_misc.c:101-322) for one ref_viewpass_t, with the reference's float
+ * expression order and this host's libm (tgmath: tan on a float argument is tanf).
+ */
+static void rc_setup_view( const ref_viewpass_t *rvp, rc_view_t *v )
+{
+	vec3_t vforward, vright, vup;
+	memset( v, 0, sizeof( *v ));
+
+	AngleVectors( rvp->viewangles, vforward, vright, vup );
+	VectorCopy( rvp->vieworigin, v->origin );
+	VectorCopy( vforward, v->vforward ); VectorCopy( vright, v->vright ); VectorCopy( vup, v->vup );
+
+	int x = rvp->viewport[0], y = rvp->viewport[1], w = rvp->viewport[2], h = rvp->viewport[3];
+	v->vrect[0] = x; v->vrect[1] = y; v->vrect[2] = w; v->vrect[3] = h;
+
+	float horizontalFieldOfView = 2 * tan((float)rvp->fov_x / 360.0f * M_PI_F );
+	float verticalFieldOfView = 2 * tan((float)rvp->fov_y / 360.0f * M_PI_F );
+
+	int vrectright = x + w, vrectbottom = y + h;
+	v->fvrectx_adj = (float)x - 0.5f;
+	v->vrect_x_adj_shift20 = ( x << 20 ) + ( 1 << 19 ) - 1;
+	v->fvrecty_adj = (float)y - 0.5f;
+	v->vrectright_adj_shift20 = ( vrectright << 20 ) + ( 1 << 19 ) - 1;
+	v->fvrectright_adj = (float)vrectright - 0.5f;
+	v->fvrectbottom_adj = (float)vrectbottom - 0.5f;
+
+	float xOrigin = 0.5f, yOrigin = 0.5f; /* XCENTERING, YCENTERING */
+	v->xcenter = ((float)w * 0.5f ) + x - 0.5f;
+	v->ycenter = ((float)h * 0.5f ) + y - 0.5f;
+	v->xscale = w / horizontalFieldOfView;
+	v->xscaleinv = 1.0f / v->xscale;
+	v->yscale = v->xscale;
+	v->yscaleinv = 1.0f / v->yscale;
+
+	vec3_t screenedge[4];
+	screenedge[0][0] = -1.0f / ( xOrigin * horizontalFieldOfView ); screenedge[0][1] = 0; screenedge[0][2] = 1;
+	screenedge[1][0] = 1.0f / (( 1.0f - xOrigin ) * horizontalFieldOfView ); screenedge[1][1] = 0; screenedge[1][2] = 1;
+	screenedge[2][0] = 0; screenedge[2][1] = -1.0f / ( yOrigin * verticalFieldOfView ); screenedge[2][2] = 1;
+	screenedge[3][0] = 0; screenedge[3][1] = 1.0f / (( 1.0f - yOrigin ) * verticalFieldOfView ); screenedge[3][2] = 1;
+	for( int i = 0; i < 4; i++ )
+		VectorNormalize( screenedge[i] );
+
+	/* R_TransformFrustum */
+	for( int i = 0; i < 4; i++ )
+	{
+		vec3_t t, v2;
+		t[0] = screenedge[i][2];
+		t[1] = -screenedge[i][0];
+		t[2] = screenedge[i][1];
+		v2[0] = t[1] * vright[0] + t[2] * vup[0] + t[0] * vforward[0];
+		v2[1] = t[1] * vright[1] + t[2] * vup[1] + t[0] * vforward[1];
+		v2[2] = t[1] * vright[2] + t[2] * vup[2] + t[0] * vforward[2];
+		VectorCopy( v2, v->clip_normal[i] );
+		v->clip_dist[i] = DotProduct( rvp->vieworigin, v2 );
+	}
+	/* R_SetUpFrustumIndexes */
+	for( int i = 0; i < 4; i++ )
+		for( int j = 0; j < 3; j++ )
+		{
+			if( v->clip_normal[i][j] < 0 ) { v->frustum_idx[i][j] = j; v->frustum_idx[i][j + 3] = j + 3; }
+			else { v->frustum_idx[i][j] = j + 3; v->frustum_idx[i][j + 3] = j; }
+		}
+
+	/* D_ViewChanged + d_setup */
+	v->scale_for_mip = v->xscale;
+	if( v->yscale > v->xscale ) v->scale_for_mip = v->yscale;
+	int minmip = sw_mipcap.value;
+	v->minmip = minmip > 3 ? 3 : ( minmip < 0 ? 0 : minmip );
+	static const float basemip[3] = { 1.0, 0.5 * 0.8, 0.25 * 0.8 };
+	for( int i = 0; i < 3; i++ )
+		v->scalemip[i] = basemip[i] * sw_mipscale.value;
+
+	/* D_DrawSurfaces: transformed_modelorg = TransformVector( vieworigin - vec3_origin ) */
+	vec3_t modelorg;
+	VectorSubtract( rvp->vieworigin, vec3_origin, modelorg );
+	v->modelorg_t[0] = DotProduct( modelorg, vright );
+	v->modelorg_t[1] = DotProduct( modelorg, vup );
+	v->modelorg_t[2] = DotProduct( modelorg, vforward );
+
+	v->turb_phase = (int)( gp_cl->time * 20 ) & 127; /* SPEED, CYCLE */
+	v->sky_color = (int)sw_clearcolor.value & 0xFFFF;
+	v->flags = rvp->flags;
+	v->pvs_radius = r_novis.value ? -1.0f : r_pvs_radius->value;
+}
+
+/* ---------------------------------------------------------------------------------------------- */
+/* frames: views queue up between R_BeginFrame and R_EndFrame and are rendered as one batch          */
+
+static void rc_prepare_batch( void )
+{
+	if( !rc.scene_valid )
+		gEngfuncs.Host_Error( "ref_cuda: render without a world (R_NewMap not called)\n" );
+	rc_sync_textures();
+	rc_resolve_texnums( false );
+	RC_CHECK_DEV( rc_dev_set_lightstyles( rc.lightstylevalue ));
+}
+
+static void rc_queue_view( const ref_viewpass_t *rvp )
+{
+	if( rc.nviews == rc.maxviews )
+	{
+		int n = rc.maxviews ? rc.maxviews * 2 : 64;
+		rc.views = gEngfuncs._Mem_Realloc( rc.pool, rc.views, sizeof( rc_view_t ) * n, true, __FILE__, __LINE__ );
+		rc.maxviews = n;
+	}
+	rc_setup_view( rvp, &rc.views[rc.nviews++] );
+}
+
+static void rc_ensure_framebuf( void )
+{
+	int w = gpGlobals->width, h = gpGlobals->height;
+	if( rc.framebuf && rc.fb_w == w && rc.fb_h == h )
+		return;
+	rc_free( rc.framebuf ); rc_free( rc.zbuf );
+	rc.framebuf = rc_malloc((size_t)w * h * 2 );
+	rc.zbuf = rc_malloc((size_t)w * h * 2 );
+	rc.fb_w = w; rc.fb_h = h;
+}
+
+static void R_BeginFrame( qboolean clearScene ) { (void)clearScene; rc.nviews = 0; }
+
+/* GL_RenderFrame slot == R_RenderFrame (ref/soft/r_main.c:1141): here the view is only recorded */
+static void R_RenderFrame( const ref_viewpass_t *rvp )
+{
+	if( !FBitSet( rvp->flags, RF_DRAW_WORLD ))
+		return; /* menu / model-viewer passes have no world; entity-only views arrive with the studio path */
+	rc_queue_view( rvp );
+}
+
+static void R_RenderScene( void ) {}
+
+/* pixel_t -> display format of the engine's software surface (R_BuildScreenMap + R_BlitScreen,
+ * ref/soft/r_glblit.c:347-407,591-721) for the first queued view */
+static uint rc_mask_shift( uint m ) { uint s = 0; if( !m ) return 0; while( !( m & 1 )) { m >>= 1; s++; } return s; }
+static uint rc_mask_bits( uint m ) { uint c = 0; while( m ) { c += m & 1; m >>= 1; } return c; }
+
+static void rc_blit_screen( void )
+{
+	void *dst = gEngfuncs.SW_LockBuffer();
+	if( !dst )
+		return;
+	uint rs = rc_mask_shift( rc.sw_r ), gs = rc_mask_shift( rc.sw_g ), bs = rc_mask_shift( rc.sw_b );
+	uint rm = 1u << rc_mask_bits( rc.sw_r ), gm = 1u << rc_mask_bits( rc.sw_g ), bm = 1u << rc_mask_bits( rc.sw_b );
+	int w = rc.fb_w, h = rc.fb_h;
+	for( int y = 0; y < h; y++ )
+		for( int x = 0; x < w; x++ )
+		{
+			uint r, g, b;
+			rc_decode565( rc.framebuf[y * w + x], &r, &g, &b );
+			/* major and minor parts are scaled separately and or-ed, as the reference's table does */
+			uint rM = r & ~3u, gM = g & ~7u, bM = b & ~7u;
+			uint px = (( rM * rm / 31 ) << rs | ( gM * gm / 63 ) << gs | ( bM * bm / 31 ) << bs )
+				| ((( r & 3 ) * rm / 31 ) << rs | (( g & 7 ) * gm / 63 ) << gs | (( b & 7 ) * bm / 31 ) << bs );
+			if( rc.sw_bpp == 2 ) ((uint16_t *)dst )[y * rc.sw_stride + x] = (uint16_t)px;
+			else ((uint32_t *)dst )[y * rc.sw_stride + x] = px;
+		}
+	gEngfuncs.SW_UnlockBuffer();
+}
+
+static void R_EndFrame( void )
+{
+	if( rc.nviews > 0 && rc.scene_valid )
+	{
+		int w = gpGlobals->width, h = gpGlobals->height;
+		rc_prepare_batch();
+		rc_ensure_framebuf();
+		if( rc.nviews == 1 )
+		{
+			RC_CHECK_DEV( rc_dev_render( rc.views, 1, w, h, 0, rc.framebuf, rc.zbuf ));
+		}
+		else
+		{
+			/* several passes in one frame share the screen in the reference; composite their viewports */
+			size_t px = (size_t)w * h;
+			uint16_t *all = rc_malloc( px * 2 * rc.nviews );
+			RC_CHECK_DEV( rc_dev_render( rc.views, rc.nviews, w, h, 0, all, NULL ));
+			for( int i = 0; i < rc.nviews; i++ )
+			{
+				const int *vr = rc.views[i].vrect;
+				for( int y = vr[1]; y < vr[1] + vr[3] && y < h; y++ )
+					memcpy( rc.framebuf + (size_t)y * w + vr[0], all + px * i + (size_t)y * w + vr[0], (size_t)Q_min( vr[2], w - vr[0] ) * 2 );
+			}
+			rc_free( all );
+		}
+		rc_blit_screen();
+	}
+	rc.nviews = 0;
+}
+
+/* ---- batch extension (include/ref_cuda.h) ---- */
+
+int RefCuda_RenderViews( const ref_viewpass_t *views, int nviews, unsigned short *color_out, short *z_out, int clear )
+{
+	if( !rc.initialized || nviews <= 0 )
+		return -1;
+	rc_prepare_batch();
+	rc.nviews = 0;
+	for( int i = 0; i < nviews; i++ )
+		rc_queue_view( &views[i] );
+	int r = rc_dev_render( rc.views, rc.nviews, gpGlobals->width, gpGlobals->height, clear, color_out, z_out );
+	rc.nviews = 0;
+	if( r != 0 )
+		gEngfuncs.Host_Error( "ref_cuda: rc_dev_render failed: %s\n", rc_dev_last_error());
+	return r;
+}
+
+int RefCuda_BenchResident( int iters, int rebuild_cache, float *ms_total, float *ms_stage )
+{
+	return rc_dev_bench_resident( iters, rebuild_cache, ms_total, ms_stage );
+}
+
+int RefCuda_ReadSurfaceCache( int surf, int mip, unsigned short *out, int maxtexels, int *width, int *height, int *valid )
+{
+	return rc_dev_read_cache_block( surf, mip, out, maxtexels, width, height, valid );
+}
+
+int RefCuda_GetCounters( unsigned long long *out, int n ) { return rc_dev_read_counters((uint64_t *)out, n ); }
+unsigned long long RefCuda_LaunchCount( void ) { return rc_dev_launch_count(); }
+const char *RefCuda_DeviceName( void ) { return rc_dev_name(); }
+
+/* ---------------------------------------------------------------------------------------------- */
+/* init / shutdown                                                                                  */
+
+static qboolean R_Init( void )
+{
+	gEngfuncs.Cvar_RegisterVariable( &sw_clearcolor );
+	gEngfuncs.Cvar_RegisterVariable( &sw_mipcap );
+	gEngfuncs.Cvar_RegisterVariable( &sw_mipscale );
+	gEngfuncs.Cvar_RegisterVariable( &sw_noalphabrushes );
+	gEngfuncs.Cvar_RegisterVariable( &cu_device );
+	gEngfuncs.Cvar_RegisterVariable( &r_novis );
+
+	rc.pool = gEngfuncs._Mem_AllocPool( "ref_cuda zone", 0, __FILE__, __LINE__ );
+
+	if( !gEngfuncs.R_Init_Video( REF_SOFTWARE ))
+	{
+		gEngfuncs.R_Free_Video();
+		gEngfuncs.Con_Printf( S_ERROR "ref_cuda: can't initialize video subsystem\n" );
+		return false;
+	}
+
+	/* no CPU path exists behind this plugin: without a usable CUDA device initialisation fails */
+	if( rc_dev_init((int)cu_device.value ) != 0 )
+	{
+		gEngfuncs.Con_Printf( S_ERROR "ref_cuda: CUDA initialisation failed: %s\n", rc_dev_last_error());
+		gEngfuncs.R_Free_Video();
+		return false;
+	}
+
+	rc.lightgamma = (const uint16_t *)gEngfuncs.EngineGetParm( PARM_GET_LIGHTGAMMATABLE_PTR, 0 );
+	static uint16_t identity[1024];
+	if( !rc.lightgamma || FBitSet( gp_host->features, ENGINE_LINEAR_GAMMA_SPACE ))
+	{
+		for( int i = 0; i < 1024; i++ ) identity[i] = i; /* LightToTexGamma is the identity then (r_local.h:518) */
+		rc.lightgamma = identity;
+	}
+
+	rc_build_colormap();
+	for( int i = 0; i < 1280; i++ ) /* R_InitTurb, ref/soft/r_main.c:1312: AMP + sin( i * 3.14159 * 2 / CYCLE ) * AMP */
+		rc.sintable[i] = ( 8 * 0x10000 ) + sin( i * 3.14159 * 2 / 128 ) * ( 8 * 0x10000 );
+	RC_CHECK_DEV( rc_dev_upload_luts( rc.colormap, rc.lightgamma, rc.sintable ));
+
+	if( gpGlobals->width < 128 ) gpGlobals->width = 128;
+	if( gpGlobals->height < 128 ) gpGlobals->height = 128;
+	if( !gEngfuncs.SW_CreateBuffer( gpGlobals->width, gpGlobals->height, &rc.sw_stride, &rc.sw_bpp, &rc.sw_r, &rc.sw_g, &rc.sw_b ))
+		return false;
+
+	/* texture slot 0 is never handed out (r_image.c:859) */
+	memset( rc.images, 0, sizeof( rc.images ));
+	rc_strncpy( rc.images[0].name, "*unused*", sizeof( rc.images[0].name ));
+	rc.numImages = 1;
+
+	/* GL_InitRandomTable, ref/common/ref_context.c:46-56 */
+	for( int tu = 0; tu < MOD_FRAMES; tu++ )
+		for( int tv = 0; tv < MOD_FRAMES; tv++ )
+			rc_rtable[tu][tv] = gEngfuncs.COM_RandomLong( 0, 0x7FFF );
+	gEngfuncs.COM_SetRandomSeed( 0 );
+
+	for( int i = 0; i < MAX_LIGHTSTYLES; i++ ) rc.lightstylevalue[i] = 256;
+	rc.initialized = true;
+	gEngfuncs.Con_Printf( "ref_cuda: rendering on %s\n", rc_dev_name());
+	return true;
+}
+
+static void R_Shutdown( void )
+{
+	if( !rc.initialized )
+		return;
+	rc_dev_shutdown();
+	gEngfuncs.R_Free_Video();
+	gEngfuncs._Mem_FreePool( &rc.pool, __FILE__, __LINE__ );
+	memset( &rc, 0, sizeof( rc ));
+}
+
+static const char *R_GetConfigName( void ) { return "ref_cuda"; }
+
+/* ---------------------------------------------------------------------------------------------- */
+/* the remaining ref_interface_t slots.  Every slot is non-NULL (the engine calls most of them
+ * unconditionally); the ones ref_soft itself leaves empty (ref/soft/r_context.c:23-26,266-375) are
+ * empty here too.  Entity, studio, sprite, decal and 2D slots accept their calls and are wired to
+ * the GPU path as those stages land. */
+
+static qboolean R_SetDisplayTransform( ref_screen_rotation_t rotate, int x, int y, float sx, float sy )
+{
+	(void)x; (void)y; (void)sx; (void)sy;
+	return rotate == REF_ROTATE_NONE;
+}
+static void GL_SetupAttributes( int safegl ) { (void)safegl; }
+static void GL_InitExtensions( void ) {}
+static void GL_ClearExtensions( void ) {}
+static void R_GammaChanged( qboolean do_reset_gamma ) { if( !do_reset_gamma ) rc_dev_flush_cache(); }
+static void R_PushScene( void ) {}
+static void R_PopScene( void ) {}
+static void GL_BackendStartFrame( void ) {}
+static void GL_BackendEndFrame( void ) {}
+static void R_ClearScreen( void ) {}
+static void R_AllowFog( qboolean allow ) { (void)allow; }
+static void GL_SetRenderMode( int renderMode ) { (void)renderMode; }
+static qboolean R_AddEntity( struct cl_entity_s *clent, int type ) { (void)clent; (void)type; return true; }
+static void R_ProcessEntData( qboolean allocate, cl_entity_t *entities, unsigned int max_entities ) { (void)allocate; (void)entities; (void)max_entities; }
+static void R_ShowTextures( void ) {}
+static const byte *R_GetTextureOriginalBuffer( unsigned int idx ) { (void)idx; return NULL; }
+static void GL_ProcessTexture( int texnum, float gamma, int topColor, int bottomColor ) { (void)texnum; (void)gamma; (void)topColor; (void)bottomColor; }
+static void R_SetupSky( int *skyboxTextures ) { (void)skyboxTextures; }
+static void R_Set2DMode( qboolean enable ) { (void)enable; }
+static void R_DrawStretchPic( float x, float y, float w, float h, float s1, float t1, float s2, float t2, int texnum )
+{ (void)x; (void)y; (void)w; (void)h; (void)s1; (void)t1; (void)s2; (void)t2; (void)texnum; }
+static void FillRGBA( int rendermode, float x, float y, float w, float h, byte r, byte g, byte b, byte a )
+{ (void)rendermode; (void)x; (void)y; (void)w; (void)h; (void)r; (void)g; (void)b; (void)a; }
+static int WorldToScreen( const vec3_t world, vec3_t screen ) { (void)world; VectorClear( screen ); return 1; }
+static qboolean VID_ScreenShot( const char *filename, int shot_type ) { (void)filename; (void)shot_type; return false; }
+static qboolean VID_CubemapShot( const char *base, uint size, const float *vieworg, qboolean skyshot ) { (void)base; (void)size; (void)vieworg; (void)skyshot; return false; }
+static colorVec R_LightPoint( const float *p ) { colorVec c = { 255, 255, 255, 255 }; (void)p; return c; }
+static void R_DecalShoot( int textureIndex, int entityIndex, int modelIndex, vec3_t pos, int flags, float scale )
+{ (void)textureIndex; (void)entityIndex; (void)modelIndex; (void)pos; (void)flags; (void)scale; }
+static void R_DecalRemoveAll( int texture ) { (void)texture; }
+static int R_CreateDecalList( struct decallist_s *pList ) { (void)pList; return 0; }
+static void R_ClearAllDecals( void ) {}
+static float R_StudioEstimateFrame( cl_entity_t *e, mstudioseqdesc_t *pseqdesc, double time ) { (void)e; (void)pseqdesc; (void)time; return 0.0f; }
+static void R_StudioLerpMovement( cl_entity_t *e, double time, vec3_t origin, vec3_t angles ) { (void)time; VectorCopy( e->origin, origin ); VectorCopy( e->angles, angles ); }
+static qboolean R_StudioFillAPI( struct engine_studio_api_s *api, struct r_studio_interface_s *pDefaultDraw ) { (void)api; (void)pDefaultDraw; return false; }
+static void R_StudioSetDrawInterface( struct r_studio_interface_s *pDraw ) { (void)pDraw; }
+static void R_SetSkyCloudsTextures( int solidskyTexture, int alphaskyTexture ) { (void)solidskyTexture; (void)alphaskyTexture; }
+static void GL_SubdivideSurface( model_t *mod, msurface_t *fa ) { (void)mod; (void)fa; }
+static qboolean Mod_ProcessRenderData( model_t *mod, qboolean create, const byte *buffer, size_t buffersize )
+{
+	(void)buffer; (void)buffersize;
+	if( create && mod->type != mod_brush && mod->type != mod_studio && mod->type != mod_sprite && mod->type != mod_alias )
+		return false;
+	return true;
+}
+static void Mod_StudioLoadTextures( model_t *mod, void *data ) { (void)mod; (void)data; }
+static void CL_DrawParticles( double frametime, particle_t *particles, float partsize ) { (void)frametime; (void)particles; (void)partsize; }
+static void CL_DrawTracers( double frametime, particle_t *tracers ) { (void)frametime; (void)tracers; }
+static void CL_DrawBeams( int fTrans, BEAM *beams ) { (void)fTrans; (void)beams; }
+
+static intptr_t RefGetParm( int parm, int arg )
+{
+	rc_image_t *t = ( arg >= 0 && arg < RC_MAX_TEXTURES ) ? &rc.images[arg] : &rc.images[0];
+	switch( parm )
+	{
+	case PARM_TEX_WIDTH: return t->width;
+	case PARM_TEX_HEIGHT: return t->height;
+	case PARM_TEX_SRC_WIDTH: return t->srcWidth;
+	case PARM_TEX_SRC_HEIGHT: return t->srcHeight;
+	case PARM_TEX_MIPCOUNT: return t->pixels[0] ? 4 : 0;
+	case PARM_TEX_DEPTH: return 1;
+	case PARM_TEX_FLAGS: return t->flags;
+	case PARM_LIGHTSTYLEVALUE: return rc.lightstylevalue[bound( 0, arg, MAX_LIGHTSTYLES - 1 )];
+	case PARM_GL_CONTEXT_TYPE: return CONTEXT_TYPE_SOFTWARE;
+	case PARM_NUMENTITIES: return 0;
+	default: return 0;
+	}
+}
+
+static void R_GetDetailScaleForTexture( int texture, float *xScale, float *yScale ) { (void)texture; if( xScale ) *xScale = 1.0f; if( yScale ) *yScale = 1.0f; }
+static void R_SetDetailScaleForTexture( int texture, float xScale, float yScale ) { (void)texture; (void)xScale; (void)yScale; }
+static void R_OverrideTextureSourceSize( unsigned int texnum, unsigned int srcWidth, unsigned int srcHeight )
+{
+	if( texnum < RC_MAX_TEXTURES ) { rc.images[texnum].srcWidth = srcWidth; rc.images[texnum].srcHeight = srcHeight; }
+}
+static void GL_UpdateTexture( int texnum, int cols, int rows, int width, int height, const byte *buffer, pixformat_t fmt )
+{ (void)texnum; (void)cols; (void)rows; (void)width; (void)height; (void)buffer; (void)fmt; }
+static void GL_Bind( int tmu, unsigned int texnum ) { (void)tmu; (void)texnum; }
+static void GL_OrthoBounds( const float *mins, const float *maxs ) { (void)mins; (void)maxs; }
+
+static qboolean R_SpeedsMessage( char *out, size_t size )
+{
+	uint64_t c[RC_CTR_COUNT];
+	if( !r_speeds->value || rc_dev_read_counters( c, RC_CTR_COUNT ) != 0 )
+		return false;
+	snprintf( out, size, "ref_cuda: %llu views %llu faces %llu edges %llu spans, %llu cache blocks built\n",
+		(unsigned long long)c[RC_CTR_VIEWS], (unsigned long long)c[RC_CTR_SURFS], (unsigned long long)c[RC_CTR_EDGES],
+		(unsigned long long)c[RC_CTR_SPANS], (unsigned long long)c[RC_CTR_CACHE_BLOCKS] );
+	return true;
+}
+static byte *Mod_GetCurrentVis( void ) { return NULL; }
+static void R_ClearScene( void ) {}
+static void TriRenderMode( int mode ) { (void)mode; }
+static void TriBegin( int primitiveCode ) { (void)primitiveCode; }
+static void TriEnd( void ) {}
+static void TriColor4f( float r, float g, float b, float a ) { (void)r; (void)g; (void)b; (void)a; }
+static void TriColor4ub( unsigned char r, unsigned char g, unsigned char b, unsigned char a ) { (void)r; (void)g; (void)b; (void)a; }
+static void TriVertex3fv( const float *worldPnt ) { (void)worldPnt; }
+static void TriVertex3f( float x, float y, float z ) { (void)x; (void)y; (void)z; }
+static void TriCullFace( TRICULLSTYLE mode ) { (void)mode; }
+static void R_FillRenderAPI( struct render_api_s *api ) { (void)api; }
+static void R_FillTriAPI( struct triangleapi_s *api ) { (void)api; }
+static void VGUI_SetupDrawing( qboolean rect ) { (void)rect; }
+
+/* designated initialisers: the slot order is the ABI (engine/ref_api.h:527-658), names keep it checkable */
+static const ref_interface_t gReffuncs =
+{
+	.R_Init = R_Init, .R_Shutdown = R_Shutdown, .R_GetConfigName = R_GetConfigName, .R_SetDisplayTransform = R_SetDisplayTransform,
+	.GL_SetupAttributes = GL_SetupAttributes, .GL_InitExtensions = GL_InitExtensions, .GL_ClearExtensions = GL_ClearExtensions,
+	.R_GammaChanged = R_GammaChanged, .R_BeginFrame = R_BeginFrame, .R_RenderScene = R_RenderScene, .R_EndFrame = R_EndFrame,
+	.R_PushScene = R_PushScene, .R_PopScene = R_PopScene, .GL_BackendStartFrame = GL_BackendStartFrame, .GL_BackendEndFrame = GL_BackendEndFrame,
+	.R_ClearScreen = R_ClearScreen, .R_AllowFog = R_AllowFog, .GL_SetRenderMode = GL_SetRenderMode,
+	.R_AddEntity = R_AddEntity, .R_ProcessEntData = R_ProcessEntData, .R_ShowTextures = R_ShowTextures,
+	.R_GetTextureOriginalBuffer = R_GetTextureOriginalBuffer, .GL_LoadTextureFromBuffer = GL_LoadTextureFromBuffer,
+	.GL_ProcessTexture = GL_ProcessTexture, .R_SetupSky = R_SetupSky,
+	.R_Set2DMode = R_Set2DMode, .R_DrawStretchPic = R_DrawStretchPic, .FillRGBA = FillRGBA, .WorldToScreen = WorldToScreen,
+	.VID_ScreenShot = VID_ScreenShot, .VID_CubemapShot = VID_CubemapShot, .R_LightPoint = R_LightPoint,
+	.R_DecalShoot = R_DecalShoot, .R_DecalRemoveAll = R_DecalRemoveAll, .R_CreateDecalList = R_CreateDecalList, .R_ClearAllDecals = R_ClearAllDecals,
+	.R_StudioEstimateFrame = R_StudioEstimateFrame, .R_StudioLerpMovement = R_StudioLerpMovement,
+	.R_StudioFillAPI = R_StudioFillAPI, .R_StudioSetDrawInterface = R_StudioSetDrawInterface,
+	.R_SetSkyCloudsTextures = R_SetSkyCloudsTextures, .GL_SubdivideSurface = GL_SubdivideSurface, .CL_RunLightStyles = CL_RunLightStyles,
+	.Mod_ProcessRenderData = Mod_ProcessRenderData, .Mod_StudioLoadTextures = Mod_StudioLoadTextures,
+	.CL_DrawParticles = CL_DrawParticles, .CL_DrawTracers = CL_DrawTracers, .CL_DrawBeams = CL_DrawBeams,
+	.RefGetParm = RefGetParm,
+	.R_GetDetailScaleForTexture = R_GetDetailScaleForTexture, .R_SetDetailScaleForTexture = R_SetDetailScaleForTexture,
+	.GL_CreateTexture = GL_CreateTexture, .GL_FindTexture = GL_FindTexture, .GL_TextureName = GL_TextureName, .GL_TextureData = GL_TextureData,
+	.GL_LoadTexture = GL_LoadTexture, .GL_FreeTexture = GL_FreeTexture, .R_OverrideTextureSourceSize = R_OverrideTextureSourceSize,
+	.GL_UpdateTexture = GL_UpdateTexture, .GL_Bind = GL_Bind,
+	.GL_RenderFrame = R_RenderFrame, .GL_OrthoBounds = GL_OrthoBounds, .R_SpeedsMessage = R_SpeedsMessage,
+	.Mod_GetCurrentVis = Mod_GetCurrentVis, .R_NewMap = R_NewMap, .R_ClearScene = R_ClearScene,
+	.TriRenderMode = TriRenderMode, .Begin = TriBegin, .End = TriEnd, .Color4f = TriColor4f, .Color4ub = TriColor4ub,
+	.Vertex3fv = TriVertex3fv, .Vertex3f = TriVertex3f, .CullFace = TriCullFace,
+	.R_FillRenderAPI = R_FillRenderAPI, .R_FillTriAPI = R_FillTriAPI, .VGUI_SetupDrawing = VGUI_SetupDrawing,
+};
+
+/* engine/ref_api.h:660; handshake as ref/common/ref_context.c:57-81 */
+int GetRefAPI( int version, ref_interface_t *funcs, ref_api_t *engfuncs, ref_globals_t *globals )
+{
+	if( version != REF_API_VERSION )
+		return 0;
+
+	*funcs = gReffuncs;
+	gEngfuncs = *engfuncs;
+	gpGlobals = globals;
+
+	gp_cl = (ref_client_t *)gEngfuncs.EngineGetParm( PARM_GET_CLIENT_PTR, 0 );
+	gp_host = (ref_host_t *)gEngfuncs.EngineGetParm( PARM_GET_HOST_PTR, 0 );
+
+	RETRIEVE_ENGINE_SHARED_CVAR_LIST();
+
+	return REF_API_VERSION;
+}

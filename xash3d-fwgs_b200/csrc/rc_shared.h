@@ -1,0 +1,198 @@
+/*
+ * rc_shared.h - plain-old-data layouts shared by the C host side of ref_cuda (rc_host.c, engine
+ * headers, gcc) and the CUDA side (rc_device.cu, nvcc).  No engine types here: the host flattens
+ * model_t / msurface_t / mnode_t / mleaf_t (common/com_model.h) into these SoA-friendly records
+ * once per R_NewMap and uploads them; kernels never see an engine pointer.
+ *
+ * Naming follows the reference's domain (ref/soft/r_local.h): surfaces, edges, spans, surface
+ * cache blocks, light styles.
+ */
+#ifndef RC_SHARED_H
+#define RC_SHARED_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RC_MAXLIGHTMAPS 4
+#define RC_NUM_MIPS     4
+
+/* msurface_t.flags bits the path looks at (common/com_model.h:227-241) */
+#define RC_SURF_PLANEBACK   ( 1u << 1 )
+#define RC_SURF_DRAWSKY     ( 1u << 2 )
+#define RC_SURF_DRAWTURB    ( 1u << 4 )
+#define RC_SURF_DRAWTILED   ( 1u << 5 )
+#define RC_SURF_CONVEYOR    ( 1u << 6 )
+#define RC_SURF_TRANSPARENT ( 1u << 8 )
+
+#define RC_TRANSPARENT_COLOR 0x0349 /* ref/soft/r_local.h:588 */
+#define RC_CONTENTS_SOLID    ( -2 )
+
+typedef struct
+{
+	float normal[3];
+	float dist;
+	int32_t type; /* 0,1,2 = axial (common/bspfile.h PLANE_X..Z), else general */
+	int32_t pad[3];
+} rc_plane_t; /* 32 B */
+
+/* children: >= 0 node index, < 0 -> leaf index = -1 - child (BSP30 disk convention, common/bspfile.h:259) */
+typedef struct
+{
+	int32_t plane;
+	int32_t child[2];
+	int32_t parent; /* -1 for the root */
+	int32_t firstsurface, numsurfaces;
+	float   minmaxs[6];
+} rc_node_t; /* 48 B */
+
+typedef struct
+{
+	int32_t contents;
+	int32_t cluster;
+	int32_t parent; /* node index */
+	int32_t firstmark, nummark;
+	int32_t visofs; /* byte offset into visdata, -1 = no row (all visible) */
+	float   minmaxs[6];
+} rc_leaf_t; /* 48 B */
+
+typedef struct
+{
+	int32_t plane;
+	uint32_t flags;
+	int32_t firstedge, numedges;
+	int32_t texnum;      /* index into rc_texture_t table (R_TextureAnimation resolved on host per timestamp) */
+	int32_t lightofs;    /* color24 index into lightdata (msurface_t.samples - lightdata), -1 = none */
+	int32_t sample_size; /* Mod_SampleSizeForFace */
+	uint8_t styles[RC_MAXLIGHTMAPS];
+	int16_t texturemins[2], extents[2];
+	int16_t lightmapmins[2], lightextents[2];
+	float   lmvecs[2][4]; /* mextrasurf_t.lmvecs (texinfo vecs for plain faces) */
+	int32_t texflags;     /* mtexinfo_t.flags */
+	int32_t cache_ofs[RC_NUM_MIPS]; /* texel offset of the (face,mip) block in the surface cache arena */
+	int32_t pad[2];
+} rc_surface_t; /* 112 B */
+
+typedef struct
+{
+	int32_t width, height;
+	int32_t ofs[RC_NUM_MIPS]; /* pixel_t offset of each mip in the texel arena */
+	int32_t alpha_ofs;        /* alpha plane (TF_HAS_ALPHA) or -1 */
+	int32_t flags;
+} rc_texture_t; /* 32 B */
+
+/* static world, device pointers (filled by rc_dev_upload_scene) */
+typedef struct
+{
+	int32_t numplanes, numnodes, numleafs, numsurfaces, nummarks, numsurfedges, numedges, numverts;
+	int32_t visbytes, visdata_len, lightdata_len, numtextures;
+	int32_t numclusters, headnode, pad0, pad1;
+	const rc_plane_t   *planes;
+	const rc_node_t    *nodes;
+	const rc_leaf_t    *leafs;
+	const rc_surface_t *surfaces;
+	const int32_t      *marksurfaces;
+	const int32_t      *surfedges;
+	const uint16_t     *edges;     /* 2 vertex indices per edge */
+	const float        *verts;     /* 3 floats per vertex */
+	const uint8_t      *visdata;
+	const uint8_t      *lightdata; /* color24 */
+	const rc_texture_t *textures;
+	const uint16_t     *texels;    /* pixel_t arena */
+	const uint16_t     *colormap;  /* [32][8192], ref/soft/r_glblit.c:440 */
+	const uint16_t     *lightgamma;/* [1024] engine lightgammatable */
+	const int32_t      *sintable;  /* [1280] ref/soft/r_main.c:1312 */
+	uint16_t           *cache;     /* surface cache arena */
+} rc_scene_t;
+
+/* per-view constants: everything R_SetupFrustum/R_SetupFrameQ/R_ViewChanged/R_TransformFrustum derive
+ * (ref/soft/r_main.c:387, r_misc.c:101-322).  Computed on the host with the host libm and the reference's
+ * float expression order, so the device never re-derives a transcendental. */
+typedef struct
+{
+	float   origin[3];
+	float   vright[3], vup[3], vforward[3];
+	float   xscale, yscale, xcenter, ycenter, xscaleinv, yscaleinv;
+	float   fvrectx_adj, fvrecty_adj, fvrectright_adj, fvrectbottom_adj;
+	int32_t vrect_x_adj_shift20, vrectright_adj_shift20;
+	int32_t vrect[4];            /* x, y, width, height */
+	float   clip_normal[4][3];   /* view_clipplanes (world space) */
+	float   clip_dist[4];
+	int32_t frustum_idx[4][6];   /* reject / accept corner selectors */
+	float   scale_for_mip, scalemip[3];
+	int32_t minmip;
+	float   modelorg_t[3];       /* transformed_modelorg: TransformVector( vieworigin ) */
+	int32_t turb_phase;          /* (int)(time * SPEED) & (CYCLE - 1) */
+	int32_t sky_color;           /* (int)sw_clearcolor & 0xFFFF */
+	int32_t flags;               /* ref_viewpass_t.flags */
+	float   pvs_radius;
+	int32_t pad[1];
+} rc_view_t;
+
+/* a face the BSP walk decided to draw, in front-to-back order (R_RecursiveWorldNode -> R_RenderFace) */
+typedef struct
+{
+	int32_t surf;      /* index into rc_scene_t.surfaces */
+	int32_t clipflags; /* frustum planes still to clip against */
+} rc_cand_t;
+
+/* surf_t equivalent (ref/soft/r_local.h:805-824) + the per-surface draw state D_SolidSurf/D_CalcGradients
+ * derive (ref/soft/r_edge.c:741-813,983-1053); one per candidate, valid when .emitted != 0 */
+typedef struct
+{
+	int32_t  surf;
+	uint32_t flags;
+	int32_t  emitted;
+	int32_t  miplevel;
+	float    nearzi;
+	float    d_zistepu, d_zistepv, d_ziorigin;
+	float    d_sdivzstepu, d_tdivzstepu, d_sdivzstepv, d_tdivzstepv, d_sdivzorigin, d_tdivzorigin;
+	int32_t  sadjust, tadjust, bbextents, bbextentt;
+	int32_t  cache_ofs;  /* texel offset of the block (or of the mip-0 texture for turbulent faces) */
+	int32_t  cachewidth;
+} rc_surf_t; /* 80 B */
+
+/* edge_t equivalent (ref/soft/r_local.h:827-836): u at scanline v, stepped by u_step per line up to v2 */
+typedef struct
+{
+	int32_t  u, u_step;
+	uint32_t vv;    /* v | v2 << 16 */
+	uint32_t surfs; /* trailing (surfs[0]) | leading (surfs[1]) << 16, candidate index + 1, 0 = none */
+} rc_edge_t; /* 16 B */
+
+/* per-batch device work buffers and outputs */
+typedef struct
+{
+	int32_t nviews, width, height, pad;
+	int32_t max_cands, max_edges; /* per-view capacities */
+	const rc_view_t *views;
+	uint8_t   *leafvis;   /* [nviews][visbytes_padded] fat PVS rows (R_MarkLeaves input) */
+	uint32_t  *nodevis;   /* [nviews][nodewords] node visframe bits */
+	uint32_t  *leafmark;  /* [nviews][leafwords] leaf visframe bits */
+	uint32_t  *surfmark;  /* [nviews][surfwords] msurface_t.visframe bits */
+	int32_t   *walkstack; /* [nviews][stack_ints] explicit recursion stack */
+	rc_cand_t *cands;     /* [nviews][max_cands] */
+	rc_surf_t *surfs;     /* [nviews][max_cands] */
+	rc_edge_t *edges;     /* [nviews][max_edges] */
+	int32_t   *ncands;    /* [nviews] */
+	int32_t   *nedges;    /* [nviews] */
+	uint32_t  *cache_need;/* [numsurfaces*4 bits] (face,mip) blocks this batch samples */
+	uint16_t  *color;     /* [nviews][height][width] pixel_t */
+	int16_t   *zbuf;      /* [nviews][height][width] */
+	uint64_t  *counters;  /* RC_CTR_* */
+	int32_t   visbytes_padded, nodewords, leafwords, surfwords, stack_ints, pad2;
+} rc_batch_t;
+
+enum
+{
+	RC_CTR_VIEWS = 0, RC_CTR_PIXELS, RC_CTR_CANDS, RC_CTR_SURFS, RC_CTR_EDGES, RC_CTR_SPANS,
+	RC_CTR_CACHE_BLOCKS, RC_CTR_CACHE_TEXELS, RC_CTR_OVERFLOW_EDGES, RC_CTR_OVERFLOW_EVENTS,
+	RC_CTR_OVERFLOW_STACK, RC_CTR_OVERFLOW_CANDS, RC_CTR_COUNT = 32
+};
+
+#ifdef __cplusplus
+}
+#endif
+#endif
