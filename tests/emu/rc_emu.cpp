@@ -135,7 +135,7 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 	memset( E.counters, 0, sizeof( E.counters ));
 	E.vsurfs.assign( nviews, {} ); E.vedges.assign( nviews, {} );
 	size_t px = (size_t)width * height;
-	int stack_ints = 2 * ( sc->pad0 + 4 ) + 8;
+	int stack_ints = 2 * ( sc->maxdepth + 4 ) + 8;
 
 	for( int vi = 0; vi < nviews; vi++ )
 	{

@@ -65,6 +65,10 @@ XH_EXPORT uint64_t xh_callback_count( void );            /* engine callbacks hit
 XH_EXPORT const char *xh_last_error( void );
 /* oracle-only probe: CACHESPOT(surf)[mip] of ref_soft -> surface cache block (r_local.h:781-793,968) */
 XH_EXPORT const void *xh_soft_cache_block( int surf, int mip, int *width, int *height );
+/* oracle-only driver loop: n cameras (x y z pitch yaw roll) through ref_soft's GL_RenderFrame, buffers copied out
+ * per view; returns the seconds spent inside GL_RenderFrame (xh_probe_soft.c) */
+XH_EXPORT double xh_soft_render_views( const float *cams, int n, float fov_x, float fov_y, int w, int h, int flags, int clear,
+	unsigned short *color_out, short *z_out );
 
 #ifdef __cplusplus
 }

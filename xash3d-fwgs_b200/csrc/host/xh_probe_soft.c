@@ -23,3 +23,42 @@ const void *xh_soft_cache_block( int surf, int mip, int *width, int *height )
 	if( height ) *height = (int)c->height;
 	return c->data;
 }
+
+/*
+ * ORACLE-ONLY driver loop: renders n camera views (x y z pitch yaw roll each) one after another through
+ * the loaded ref_soft's GL_RenderFrame, the way the engine would, and copies vid.buffer / d_pzbuffer out
+ * after each.  Both buffers are zeroed before every view when clear != 0 (ref_soft never clears,
+ * r_edge.c:983) and the cached view cluster is forgotten so every view rebuilds its PVS marks
+ * (R_MarkLeaves early-out, r_main.c:1023).  Returns the seconds spent inside GL_RenderFrame only.
+ */
+#include <time.h>
+
+double xh_soft_render_views( const float *cams, int n, float fov_x, float fov_y, int w, int h, int flags, int clear,
+	unsigned short *color_out, short *z_out )
+{
+	viddef_t *pvid = (viddef_t *)xh_ref_symbol( "vid" );
+	short **pz = (short **)xh_ref_symbol( "d_pzbuffer" );
+	int *oldcluster = (int *)xh_ref_symbol( "r_oldviewcluster" );
+	if( !pvid || !pz || !oldcluster )
+		return -1.0;
+	size_t px = (size_t)pvid->width * pvid->height;
+	double total = 0;
+	for( int i = 0; i < n; i++ )
+	{
+		const float *c = cams + 6 * i;
+		struct timespec t0, t1;
+		if( clear )
+		{
+			memset( pvid->buffer, 0, px * sizeof( pixel_t ));
+			memset( *pz, 0, px * sizeof( short ));
+		}
+		*oldcluster = -2;
+		clock_gettime( CLOCK_MONOTONIC, &t0 );
+		xh_render_view( c, c + 3, fov_x, fov_y, 0, 0, w, h, flags );
+		clock_gettime( CLOCK_MONOTONIC, &t1 );
+		total += ( t1.tv_sec - t0.tv_sec ) + 1e-9 * ( t1.tv_nsec - t0.tv_nsec );
+		if( color_out ) memcpy( color_out + px * i, pvid->buffer, px * sizeof( pixel_t ));
+		if( z_out ) memcpy( z_out + px * i, *pz, px * sizeof( short ));
+	}
+	return total;
+}

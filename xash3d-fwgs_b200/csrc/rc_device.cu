@@ -1,0 +1,891 @@
+/*
+ * rc_device.cu - the sm_100a kernels of ref_cuda and the thin C layer (rc_dev.h) the plugin's C host
+ * code calls.  One batch = N independent camera views of one world at one timestamp.
+ *
+ * Stage map (reference function -> kernel), all per batch:
+ *   S0 k_viswalk      Mod_PointInLeaf/Mod_FatPVS/R_MarkLeaves + R_RecursiveWorldNode   one warp per view
+ *   S1 k_faces        R_RenderFace/R_ClipEdge/R_EmitEdge + D_CalcGradients             one thread per (view, face)
+ *      k_line_scan    active-edge count per scanline (difference array -> prefix sums)  one warp per view
+ *      k_bin_edges    R_InsertNewEdges/R_StepActiveU in closed form: edge -> events     one thread per edge
+ *   S2 k_cache_list   D_CacheSurface staleness test -> work list                        one thread per (face, mip)
+ *      k_cache_build  R_BuildLightMap + R_DrawSurface                                   persistent CTAs, one block per (face, mip)
+ *   S3 k_scanlines    R_ScanEdges/R_GenerateSpans + D_DrawSpans16/D_DrawZSpans/Turbulent8  one warp per (view, scanline)
+ *
+ * The per-item arithmetic is rc_core.h (shared with the CPU debug harness); this file is the parallel
+ * decomposition, the memory layout and the stream plumbing.  Compiled with -fmad=false and IEEE
+ * division so float set-up matches the oracle's x86-64 SSE build bit for bit.
+ */
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <vector>
+
+#include "rc_dev.h"
+#include "rc_core.h"
+
+/* ---------------------------------------------------------------------------------------------- */
+/* device-side records private to this file                                                          */
+
+struct rc_cachekey_t
+{
+	int32_t texnum;
+	int32_t light[RC_MAXLIGHTMAPS];
+	int32_t valid;
+	int32_t pad[2];
+}; /* 32 B: what D_CacheSurface compares (r_surf.c:1090-1120): texture, light style values */
+
+struct rc_work_t
+{
+	const rc_view_t *views;
+	int32_t nviews, width, height, clear;
+	int32_t max_cands, max_edges, max_events; /* per-view capacities */
+	int32_t visbytes_padded, nodewords, leafwords, surfwords, stack_ints;
+	uint8_t   *leafvis;
+	uint32_t  *nodevis, *leafmark, *surfmark;
+	int32_t   *walkstack;
+	rc_cand_t *cands;
+	rc_surf_t *surfs;
+	rc_edge_t *edges;
+	int32_t   *ncands, *nedges;
+	int32_t   *linecnt;   /* [nviews][height + 1] difference array, then active-edge count per scanline */
+	int32_t   *lineofs;   /* [nviews][height] first event of the scanline in the view's event arena */
+	int32_t   *linecur;   /* [nviews][height] fill cursor */
+	rc_event_t *events;   /* [nviews][max_events] */
+	uint32_t  *cache_need;/* [numsurfaces * 4 bits] */
+	rc_cachekey_t *cache_keys; /* [numsurfaces * 4] */
+	int32_t   *cache_list;/* [numsurfaces * 4] work list of surf * 4 + mip */
+	int32_t   *cache_nlist, *cache_cursor;
+	const int32_t *styles;/* [256] g_lightstylevalue */
+	uint16_t  *color;
+	int16_t   *zbuf;
+	unsigned long long *counters;
+};
+
+#define SCAN_WARPS   4
+#define SCAN_EVCAP   512 /* active edges per scanline the shared-memory sorter takes */
+#define SCAN_STKCAP  128 /* surface stack depth per scanline */
+#define SCAN_NEGCAP  16
+#define CACHE_THREADS 256
+#define CACHE_LUXCAP 2048
+
+/* ---------------------------------------------------------------------------------------------- */
+/* S0: visibility + BSP walk                                                                         */
+
+__global__ void __launch_bounds__( 32 ) k_viswalk( rc_scene_t sc, rc_work_t w )
+{
+	const int view = blockIdx.x, lane = threadIdx.x;
+	const rc_view_t *vw = &w.views[view];
+	uint8_t  *vis = w.leafvis + (size_t)view * w.visbytes_padded;
+	uint32_t *nodevis = w.nodevis + (size_t)view * w.nodewords;
+	uint32_t *leafmark = w.leafmark + (size_t)view * w.leafwords;
+	uint32_t *surfmark = w.surfmark + (size_t)view * w.surfwords;
+	int32_t  *stack = w.walkstack + (size_t)view * w.stack_ints;
+
+	for( int i = lane; i < w.nodewords; i += 32 ) nodevis[i] = 0;
+	for( int i = lane; i < w.leafwords; i += 32 ) leafmark[i] = 0;
+	for( int i = lane; i < w.surfwords; i += 32 ) surfmark[i] = 0;
+
+	if( vw->pvs_radius < 0 )
+	{
+		for( int i = lane; i < w.visbytes_padded; i += 32 ) vis[i] = 0xFF;
+	}
+	else if( lane == 0 )
+		rc_fat_pvs( &sc, vw->origin, vw->pvs_radius, vis, stack, w.stack_ints );
+	__syncwarp();
+
+	/* R_MarkLeaves: lanes take clusters; a lane stops climbing where another one already passed */
+	for( int i = lane; i < sc.numclusters; i += 32 )
+	{
+		if( !( vis[i >> 3] & ( 1 << ( i & 7 ))))
+			continue;
+		atomicOr( &leafmark[( i + 1 ) >> 5], 1u << (( i + 1 ) & 31 ));
+		int32_t node = sc.leafs[i + 1].parent;
+		while( node >= 0 )
+		{
+			uint32_t bit = 1u << ( node & 31 );
+			if( atomicOr( &nodevis[node >> 5], bit ) & bit )
+				break;
+			node = sc.nodes[node].parent;
+		}
+	}
+	__syncwarp();
+
+	if( lane == 0 )
+	{
+		int32_t overflow = 0;
+		int32_t n = rc_walk_world( &sc, vw, nodevis, leafmark, surfmark, stack, w.stack_ints,
+			w.cands + (size_t)view * w.max_cands, w.max_cands, &overflow );
+		w.ncands[view] = n;
+		w.nedges[view] = 0;
+		atomicAdd( &w.counters[RC_CTR_CANDS], (unsigned long long)n );
+		atomicAdd( &w.counters[RC_CTR_VIEWS], 1ull );
+		atomicAdd( &w.counters[RC_CTR_PIXELS], (unsigned long long)vw->vrect[2] * vw->vrect[3] );
+		if( overflow ) atomicAdd( &w.counters[RC_CTR_OVERFLOW_STACK], 1ull );
+	}
+	for( int i = lane; i <= w.height; i += 32 )
+		w.linecnt[(size_t)view * ( w.height + 1 ) + i] = 0;
+}
+
+/* ---------------------------------------------------------------------------------------------- */
+/* S1: faces -> surf_t records + edges                                                               */
+
+__global__ void __launch_bounds__( 128 ) k_faces( rc_scene_t sc, rc_work_t w )
+{
+	const int view = blockIdx.y;
+	const int ci = blockIdx.x * blockDim.x + threadIdx.x;
+	if( ci >= w.ncands[view] )
+		return;
+	const rc_view_t *vw = &w.views[view];
+	const rc_cand_t cand = w.cands[(size_t)view * w.max_cands + ci];
+	const rc_surface_t *sf = &sc.surfaces[cand.surf];
+	rc_surf_t *out = &w.surfs[(size_t)view * w.max_cands + ci];
+
+	/* reserve the most this face can emit: one edge per surfedge + the left re-entry edge */
+	int32_t want = sf->numedges + 1;
+	int32_t first = atomicAdd( &w.nedges[view], want );
+	rc_facestate_t fs;
+	fs.out = w.edges + (size_t)view * w.max_edges + first;
+	fs.maxout = want; fs.nout = 0;
+	fs.surfnum = (uint32_t)ci + 1;
+	if( first + want > w.max_edges )
+	{
+		fs.maxout = 0;
+		atomicAdd( &w.counters[RC_CTR_OVERFLOW_EDGES], 1ull );
+	}
+
+	rc_surf_t o;
+	o.miplevel = 0; o.cache_ofs = -1; o.cachewidth = 0;
+	o.d_zistepu = o.d_zistepv = o.d_ziorigin = 0;
+	o.d_sdivzstepu = o.d_tdivzstepu = o.d_sdivzstepv = o.d_tdivzstepv = o.d_sdivzorigin = o.d_tdivzorigin = 0;
+	o.sadjust = o.tadjust = o.bbextents = o.bbextentt = 0;
+	rc_render_face( &sc, vw, &cand, &fs, &o );
+	*out = o;
+
+	int32_t nout = fs.nout < fs.maxout ? fs.nout : fs.maxout;
+	int32_t *lc = w.linecnt + (size_t)view * ( w.height + 1 );
+	for( int32_t k = 0; k < nout; k++ )
+	{
+		uint32_t vv = fs.out[k].vv;
+		int32_t v = (int32_t)( vv & 0xFFFF ), v2 = (int32_t)( vv >> 16 );
+		if( v2 >= w.height ) v2 = w.height - 1;
+		if( v <= v2 )
+		{
+			atomicAdd( &lc[v], 1 );
+			atomicAdd( &lc[v2 + 1], -1 );
+		}
+	}
+	/* unused reservations become edges that are never active */
+	for( int32_t k = nout; k < fs.maxout; k++ )
+	{
+		fs.out[k].u = 0; fs.out[k].u_step = 0; fs.out[k].vv = 1u; fs.out[k].surfs = 0;
+	}
+
+	if( o.emitted )
+	{
+		atomicAdd( &w.counters[RC_CTR_SURFS], 1ull );
+		if( !( o.flags & ( RC_SURF_DRAWSKY | RC_SURF_DRAWTURB )) && o.cache_ofs >= 0 )
+		{
+			int32_t slot = cand.surf * 4 + o.miplevel;
+			atomicOr( &w.cache_need[slot >> 5], 1u << ( slot & 31 ));
+		}
+	}
+	atomicAdd( &w.counters[RC_CTR_EDGES], (unsigned long long)nout );
+}
+
+/* difference array -> active edges per scanline -> exclusive offsets into the view's event arena */
+__global__ void __launch_bounds__( 32 ) k_line_scan( rc_work_t w )
+{
+	const int view = blockIdx.x, lane = threadIdx.x;
+	int32_t *lc = w.linecnt + (size_t)view * ( w.height + 1 );
+	int32_t *lo = w.lineofs + (size_t)view * w.height;
+	int32_t *cur = w.linecur + (size_t)view * w.height;
+	int32_t active = 0, ofs = 0;
+	for( int base = 0; base < w.height; base += 32 )
+	{
+		int y = base + lane;
+		int32_t d = y < w.height ? lc[y] : 0;
+		/* inclusive scan of the deltas */
+		int32_t x = d;
+		for( int s = 1; s < 32; s <<= 1 )
+		{
+			int32_t t = __shfl_up_sync( 0xFFFFFFFFu, x, s );
+			if( lane >= s ) x += t;
+		}
+		int32_t cnt = active + x;
+		active += __shfl_sync( 0xFFFFFFFFu, x, 31 );
+		/* exclusive scan of the counts */
+		int32_t e = cnt;
+		for( int s = 1; s < 32; s <<= 1 )
+		{
+			int32_t t = __shfl_up_sync( 0xFFFFFFFFu, e, s );
+			if( lane >= s ) e += t;
+		}
+		if( y < w.height )
+		{
+			lc[y] = cnt;
+			lo[y] = ofs + e - cnt;
+			cur[y] = 0;
+		}
+		ofs += __shfl_sync( 0xFFFFFFFFu, e, 31 );
+	}
+	if( lane == 0 && ofs > w.max_events )
+		atomicAdd( &w.counters[RC_CTR_OVERFLOW_EVENTS], 1ull );
+}
+
+/* every edge drops one event {u at y, surfaces} into each scanline it crosses */
+__global__ void __launch_bounds__( 128 ) k_bin_edges( rc_work_t w )
+{
+	const int view = blockIdx.y;
+	const int ei = blockIdx.x * blockDim.x + threadIdx.x;
+	int32_t ne = w.nedges[view];
+	if( ne > w.max_edges ) ne = w.max_edges;
+	if( ei >= ne )
+		return;
+	const rc_edge_t e = w.edges[(size_t)view * w.max_edges + ei];
+	int32_t v = (int32_t)( e.vv & 0xFFFF ), v2 = (int32_t)( e.vv >> 16 );
+	if( v2 >= w.height ) v2 = w.height - 1;
+	const int32_t *lo = w.lineofs + (size_t)view * w.height;
+	int32_t *cur = w.linecur + (size_t)view * w.height;
+	rc_event_t *ev = w.events + (size_t)view * w.max_events;
+	uint32_t u = (uint32_t)e.u;
+	for( int32_t y = v; y <= v2; y++ )
+	{
+		int32_t slot = lo[y] + atomicAdd( &cur[y], 1 );
+		if( slot < w.max_events )
+		{
+			ev[slot].u = (int32_t)u;
+			ev[slot].surfs = e.surfs;
+		}
+		u += (uint32_t)e.u_step;
+	}
+}
+
+/* ---------------------------------------------------------------------------------------------- */
+/* S2: surface cache                                                                                 */
+
+__device__ __forceinline__ bool rc_key_stale( const rc_cachekey_t *k, const rc_surface_t *sf, const int32_t *styles )
+{
+	if( !k->valid || k->texnum != sf->texnum )
+		return true;
+	for( int j = 0; j < RC_MAXLIGHTMAPS && sf->styles[j] != 255; j++ )
+		if( k->light[j] != styles[sf->styles[j]] )
+			return true;
+	return false;
+}
+
+__global__ void __launch_bounds__( 256 ) k_cache_list( rc_scene_t sc, rc_work_t w )
+{
+	const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+	if( slot >= sc.numsurfaces * 4 )
+		return;
+	if( !(( w.cache_need[slot >> 5] >> ( slot & 31 )) & 1 ))
+		return;
+	const rc_surface_t *sf = &sc.surfaces[slot >> 2];
+	if( sf->cache_ofs[slot & 3] < 0 )
+		return;
+	if( rc_key_stale( &w.cache_keys[slot], sf, w.styles ))
+		w.cache_list[atomicAdd( w.cache_nlist, 1 )] = slot;
+}
+
+__global__ void __launch_bounds__( CACHE_THREADS ) k_cache_build( rc_scene_t sc, rc_work_t w )
+{
+	__shared__ uint32_t s_bl[CACHE_LUXCAP];
+	__shared__ int32_t s_item;
+	const int tid = threadIdx.x;
+	const int32_t nlist = *w.cache_nlist;
+
+	for( ;; )
+	{
+		__syncthreads();
+		if( tid == 0 ) s_item = atomicAdd( w.cache_cursor, 1 );
+		__syncthreads();
+		const int32_t item = s_item;
+		if( item >= nlist )
+			break;
+		const int32_t slot = w.cache_list[item];
+		const int32_t mip = slot & 3;
+		const rc_surface_t *sf = &sc.surfaces[slot >> 2];
+		const rc_texture_t *tex = &sc.textures[sf->texnum];
+		const int32_t smax = sf->lightextents[0] / sf->sample_size + 1, tmax = sf->lightextents[1] / sf->sample_size + 1;
+		const int32_t size = smax * tmax;
+		if( size > CACHE_LUXCAP )
+		{
+			if( tid == 0 ) atomicAdd( &w.counters[RC_CTR_OVERFLOW_CANDS], 1ull );
+			continue;
+		}
+		for( int32_t i = tid; i < size; i += CACHE_THREADS )
+			s_bl[i] = rc_blocklight( &sc, sf, w.styles, size, i );
+		__syncthreads();
+
+		const int32_t bw = sf->lightextents[0] >> mip, bh = sf->lightextents[1] >> mip;
+		uint16_t *dst = sc.cache + sf->cache_ofs[mip];
+		for( int32_t i = tid; i < bw * bh; i += CACHE_THREADS )
+		{
+			int32_t y = i / bw, x = i - y * bw;
+			dst[i] = rc_cache_texel( &sc, sf, tex, mip, s_bl, smax, x, y );
+		}
+		if( tid == 0 )
+		{
+			rc_cachekey_t *k = &w.cache_keys[slot];
+			k->texnum = sf->texnum;
+			for( int j = 0; j < RC_MAXLIGHTMAPS; j++ )
+				k->light[j] = sf->styles[j] != 255 ? w.styles[sf->styles[j]] : 0;
+			k->valid = 1;
+			atomicAdd( &w.counters[RC_CTR_CACHE_BLOCKS], 1ull );
+			atomicAdd( &w.counters[RC_CTR_CACHE_TEXELS], (unsigned long long)bw * bh );
+		}
+	}
+}
+
+/* ---------------------------------------------------------------------------------------------- */
+/* S3: scanlines - sort the active edges, replay them against the surface stack, draw the spans      */
+
+struct rc_scan_smem_t
+{
+	unsigned long long keys[SCAN_EVCAP];   /* sort keys, then rc_event_t in place */
+	rc_span_t spans[SCAN_EVCAP + 2];
+	int32_t   chunk0[SCAN_EVCAP + 2];      /* first chunk of each span */
+	int32_t   stk[SCAN_STKCAP], cnt[SCAN_STKCAP], neg[2 * SCAN_NEGCAP];
+	int32_t   nspans, overflow;
+};
+
+__global__ void __launch_bounds__( SCAN_WARPS * 32 ) k_scanlines( rc_scene_t sc, rc_work_t w )
+{
+	extern __shared__ __align__( 16 ) unsigned char smem_raw[];
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	rc_scan_smem_t *S = reinterpret_cast<rc_scan_smem_t *>( smem_raw ) + warp;
+
+	const int view = blockIdx.y;
+	const int y = blockIdx.x * SCAN_WARPS + warp;
+	const rc_view_t *vw = &w.views[view];
+	const int x0 = vw->vrect[0], y0 = vw->vrect[1], vw_w = vw->vrect[2], vw_h = vw->vrect[3];
+	if( y < y0 || y >= y0 + vw_h || y >= w.height )
+		return;
+
+	/* 1. this scanline's events */
+	int32_t n = w.linecnt[(size_t)view * ( w.height + 1 ) + y];
+	const int32_t ofs = w.lineofs[(size_t)view * w.height + y];
+	if( ofs + n > w.max_events ) n = w.max_events - ofs > 0 ? w.max_events - ofs : 0;
+	bool overflow = false;
+	if( n > SCAN_EVCAP ) { n = SCAN_EVCAP; overflow = true; }
+	const rc_event_t *gev = w.events + (size_t)view * w.max_events + ofs;
+	int32_t npow = 32;
+	while( npow < n ) npow <<= 1;
+	for( int i = lane; i < npow; i += 32 )
+	{
+		unsigned long long k = ~0ull;
+		if( i < n )
+		{
+			rc_event_t e = gev[i];
+			k = rc_event_key( e.u, e.surfs );
+		}
+		S->keys[i] = k;
+	}
+	__syncwarp();
+
+	/* 2. bitonic sort */
+	for( int k = 2; k <= npow; k <<= 1 )
+		for( int j = k >> 1; j > 0; j >>= 1 )
+		{
+			for( int i = lane; i < npow; i += 32 )
+			{
+				int ixj = i ^ j;
+				if( ixj > i )
+				{
+					unsigned long long a = S->keys[i], b = S->keys[ixj];
+					bool up = ( i & k ) == 0;
+					if(( a > b ) == up ) { S->keys[i] = b; S->keys[ixj] = a; }
+				}
+			}
+			__syncwarp();
+		}
+	rc_event_t *ev = reinterpret_cast<rc_event_t *>( S->keys );
+	for( int i = lane; i < n; i += 32 )
+	{
+		unsigned long long k = S->keys[i];
+		rc_event_t e;
+		e.u = (int32_t)((uint32_t)( k >> 32 ) ^ 0x80000000u );
+		e.surfs = (uint32_t)k;
+		ev[i] = e;
+	}
+	__syncwarp();
+
+	/* 3. span generation (serial replay of the sorted edges) */
+	if( lane == 0 )
+	{
+		int32_t ovf = overflow ? 1 : 0;
+		const int32_t head_iu = x0, tail_u = (( x0 + vw_w ) << 20 ) + 0xFFFFF;
+		S->nspans = rc_generate_spans( ev, n, head_iu, tail_u, S->stk, S->cnt, SCAN_STKCAP, S->neg, SCAN_NEGCAP,
+			S->spans, SCAN_EVCAP + 2, &ovf );
+		S->overflow = ovf;
+	}
+	__syncwarp();
+	const int32_t nspans = S->nspans;
+
+	/* 4. chunk table: span i owns chunks [chunk0[i], chunk0[i+1]) */
+	const rc_surf_t *vsurfs = w.surfs + (size_t)view * w.max_cands;
+	int32_t total = 0;
+	for( int base = 0; base < nspans; base += 32 )
+	{
+		int i = base + lane;
+		int32_t c = 0;
+		if( i < nspans )
+		{
+			const rc_span_t sp = S->spans[i];
+			if( sp.surf )
+				c = rc_span_nchunks( rc_span_kind( &vsurfs[sp.surf - 1] ), sp.count );
+			else if( w.clear )
+				c = ( sp.count + 7 ) >> 3;
+		}
+		int32_t x = c;
+		for( int s = 1; s < 32; s <<= 1 )
+		{
+			int32_t t = __shfl_up_sync( 0xFFFFFFFFu, x, s );
+			if( lane >= s ) x += t;
+		}
+		if( i < nspans ) S->chunk0[i] = total + x - c;
+		total += __shfl_sync( 0xFFFFFFFFu, x, 31 );
+	}
+	if( lane == 0 ) S->chunk0[nspans] = total;
+	__syncwarp();
+
+	/* 5. draw: one lane per chunk of 8 (16 for turbulent) pixels */
+	const int32_t *turb = sc.sintable + vw->turb_phase;
+	uint16_t *crow = w.color + ((size_t)view * w.height + y ) * w.width;
+	int16_t *zrow = w.zbuf + ((size_t)view * w.height + y ) * w.width;
+	for( int32_t c = lane; c < total; c += 32 )
+	{
+		int lo = 0, hi = nspans - 1;
+		while( lo < hi )
+		{
+			int mid = ( lo + hi + 1 ) >> 1;
+			if( S->chunk0[mid] <= c ) lo = mid; else hi = mid - 1;
+		}
+		const rc_span_t sp = S->spans[lo];
+		const int32_t j = c - S->chunk0[lo];
+		if( !sp.surf )
+		{
+			int32_t u = sp.u + j * 8, cnt = min( 8, sp.count - j * 8 );
+			for( int i = 0; i < cnt; i++ ) { crow[u + i] = 0; zrow[u + i] = 0; }
+			continue;
+		}
+		const rc_surf_t *sf = &vsurfs[sp.surf - 1];
+		rc_chunk_t ch;
+		rc_chunk_setup( vw, sf, vw->sky_color, sp.u, y, sp.count, j, &ch );
+		const int32_t cpx = ch.kind == RC_KIND_TURB ? 16 : 8;
+		const int32_t cnt = min( cpx, sp.count - j * cpx );
+		if( ch.kind == RC_KIND_SKY )
+		{
+			for( int i = 0; i < cnt; i++ ) { crow[ch.u0 + i] = (uint16_t)ch.base; zrow[ch.u0 + i] = rc_pixel_z( &ch, i ); }
+		}
+		else
+		{
+			const uint16_t *src = ch.kind == RC_KIND_TURB ? sc.texels : sc.cache;
+			for( int i = 0; i < cnt; i++ )
+			{
+				crow[ch.u0 + i] = src[rc_pixel_texel( &ch, i, turb )];
+				zrow[ch.u0 + i] = rc_pixel_z( &ch, i );
+			}
+		}
+	}
+	if( lane == 0 )
+	{
+		atomicAdd( &w.counters[RC_CTR_SPANS], (unsigned long long)nspans );
+		if( S->overflow ) atomicAdd( &w.counters[RC_CTR_OVERFLOW_EVENTS], 1ull );
+	}
+}
+
+/* ---------------------------------------------------------------------------------------------- */
+/* host side of the C layer                                                                          */
+
+namespace {
+
+struct Dev
+{
+	bool ready = false;
+	int device = 0;
+	char name[256] = "";
+	char err[512] = "";
+	cudaStream_t stream = nullptr;
+	cudaEvent_t ev[8] = {};
+	uint64_t launches = 0;
+
+	rc_scene_t sc{};            /* device pointers */
+	std::vector<rc_surface_t> h_surfaces;
+	int32_t h_styles[256];
+	size_t cache_texels = 0;
+	int ntextures = 0;
+	std::vector<rc_texture_t> h_textures;
+
+	/* LUTs + static arrays */
+	uint16_t *d_colormap = nullptr, *d_lightgamma = nullptr;
+	int32_t *d_sintable = nullptr;
+	rc_texture_t *d_textures = nullptr;
+	uint16_t *d_texels = nullptr;
+	void *d_scene[16] = {};
+	int32_t *d_styles = nullptr;
+	rc_cachekey_t *d_keys = nullptr;
+	uint32_t *d_need = nullptr;
+	int32_t *d_list = nullptr, *d_nlist = nullptr;
+	unsigned long long *d_counters = nullptr;
+
+	/* batch work buffers (grown on demand) */
+	rc_work_t w{};
+	int cap_views = 0, cap_w = 0, cap_h = 0;
+	rc_view_t *d_views = nullptr;
+	void *d_work[20] = {};
+	bool have_batch = false;
+} D;
+
+bool ck( cudaError_t e, const char *what )
+{
+	if( e == cudaSuccess )
+		return true;
+	snprintf( D.err, sizeof( D.err ), "%s: %s", what, cudaGetErrorString( e ));
+	return false;
+}
+#define CK( call ) do { if( !ck(( call ), #call )) return -1; } while( 0 )
+
+template <typename T> int upload( T **dst, const T *src, size_t n )
+{
+	if( *dst ) { cudaFree( *dst ); *dst = nullptr; }
+	size_t bytes = sizeof( T ) * ( n ? n : 1 );
+	CK( cudaMalloc( (void **)dst, bytes ));
+	if( n && src ) CK( cudaMemcpy( *dst, src, sizeof( T ) * n, cudaMemcpyHostToDevice ));
+	else CK( cudaMemset( *dst, 0, bytes ));
+	return 0;
+}
+
+template <typename T> int dalloc( T **dst, size_t n )
+{
+	if( *dst ) { cudaFree( *dst ); *dst = nullptr; }
+	CK( cudaMalloc( (void **)dst, sizeof( T ) * ( n ? n : 1 )));
+	return 0;
+}
+
+void free_batch()
+{
+	for( void *&p : D.d_work ) { if( p ) cudaFree( p ); p = nullptr; }
+	if( D.d_views ) { cudaFree( D.d_views ); D.d_views = nullptr; }
+	D.cap_views = 0; D.have_batch = false;
+}
+
+int ensure_batch( int nviews, int width, int height )
+{
+	if( nviews <= D.cap_views && width == D.cap_w && height == D.cap_h )
+		return 0;
+	free_batch();
+	const rc_scene_t &sc = D.sc;
+	rc_work_t &w = D.w;
+	int cap = nviews;
+	w.width = width; w.height = height;
+	w.max_cands = sc.numsurfaces < 65000 ? ( sc.numsurfaces > 0 ? sc.numsurfaces : 1 ) : 65000;
+	long long me = (long long)sc.numsurfedges + sc.numsurfaces + 64;
+	w.max_edges = (int32_t)( me < 262144 ? me : 262144 );
+	w.max_events = height * 192;
+	w.visbytes_padded = ( sc.visbytes + 15 ) & ~15;
+	w.nodewords = ( sc.numnodes + 31 ) / 32 + 1;
+	w.leafwords = ( sc.numleafs + 31 ) / 32 + 1;
+	w.surfwords = ( sc.numsurfaces + 31 ) / 32 + 1;
+	w.stack_ints = 2 * ( sc.maxdepth + 4 ) + 8;
+
+	int k = 0;
+#define WALLOC( field, type, count ) do { type *p = nullptr; if( dalloc( &p, (size_t)( count )) != 0 ) return -1; w.field = p; D.d_work[k++] = p; } while( 0 )
+	WALLOC( leafvis, uint8_t, (size_t)cap * w.visbytes_padded );
+	WALLOC( nodevis, uint32_t, (size_t)cap * w.nodewords );
+	WALLOC( leafmark, uint32_t, (size_t)cap * w.leafwords );
+	WALLOC( surfmark, uint32_t, (size_t)cap * w.surfwords );
+	WALLOC( walkstack, int32_t, (size_t)cap * w.stack_ints );
+	WALLOC( cands, rc_cand_t, (size_t)cap * w.max_cands );
+	WALLOC( surfs, rc_surf_t, (size_t)cap * w.max_cands );
+	WALLOC( edges, rc_edge_t, (size_t)cap * w.max_edges );
+	WALLOC( ncands, int32_t, cap );
+	WALLOC( nedges, int32_t, cap );
+	WALLOC( linecnt, int32_t, (size_t)cap * ( height + 1 ));
+	WALLOC( lineofs, int32_t, (size_t)cap * height );
+	WALLOC( linecur, int32_t, (size_t)cap * height );
+	WALLOC( events, rc_event_t, (size_t)cap * w.max_events );
+	WALLOC( color, uint16_t, (size_t)cap * width * height );
+	WALLOC( zbuf, int16_t, (size_t)cap * width * height );
+#undef WALLOC
+	if( dalloc( &D.d_views, cap ) != 0 ) return -1;
+	CK( cudaMemset( w.color, 0, (size_t)cap * width * height * 2 ));
+	CK( cudaMemset( w.zbuf, 0, (size_t)cap * width * height * 2 ));
+	w.views = D.d_views;
+	D.cap_views = cap; D.cap_w = width; D.cap_h = height;
+	return 0;
+}
+
+/* the device stages of one batch on D.stream; ev != NULL -> stage boundaries are recorded */
+int run_stages( bool timed )
+{
+	rc_work_t &w = D.w;
+	const rc_scene_t &sc = D.sc;
+	cudaStream_t st = D.stream;
+	w.cache_need = D.d_need; w.cache_keys = D.d_keys; w.cache_list = D.d_list;
+	w.cache_nlist = D.d_nlist; w.cache_cursor = D.d_nlist + 1;
+	w.styles = D.d_styles; w.counters = D.d_counters;
+
+	CK( cudaMemsetAsync( D.d_counters, 0, sizeof( unsigned long long ) * RC_CTR_COUNT, st ));
+	CK( cudaMemsetAsync( D.d_need, 0, sizeof( uint32_t ) * (( sc.numsurfaces * 4 + 31 ) / 32 + 1 ), st ));
+	CK( cudaMemsetAsync( D.d_nlist, 0, sizeof( int32_t ) * 2, st ));
+	if( timed ) CK( cudaEventRecord( D.ev[0], st ));
+	k_viswalk<<<w.nviews, 32, 0, st>>>( sc, w ); D.launches++;
+	if( timed ) CK( cudaEventRecord( D.ev[1], st ));
+	{
+		dim3 g(( w.max_cands + 127 ) / 128, w.nviews );
+		k_faces<<<g, 128, 0, st>>>( sc, w ); D.launches++;
+		k_line_scan<<<w.nviews, 32, 0, st>>>( w ); D.launches++;
+		dim3 g2(( w.max_edges + 127 ) / 128, w.nviews );
+		k_bin_edges<<<g2, 128, 0, st>>>( w ); D.launches++;
+	}
+	if( timed ) CK( cudaEventRecord( D.ev[2], st ));
+	{
+		int nslots = sc.numsurfaces * 4;
+		k_cache_list<<<( nslots + 255 ) / 256, 256, 0, st>>>( sc, w ); D.launches++;
+		k_cache_build<<<148 * 4, CACHE_THREADS, 0, st>>>( sc, w ); D.launches++;
+	}
+	if( timed ) CK( cudaEventRecord( D.ev[3], st ));
+	{
+		dim3 g(( w.height + SCAN_WARPS - 1 ) / SCAN_WARPS, w.nviews );
+		k_scanlines<<<g, SCAN_WARPS * 32, sizeof( rc_scan_smem_t ) * SCAN_WARPS, st>>>( sc, w ); D.launches++;
+	}
+	if( timed ) CK( cudaEventRecord( D.ev[4], st ));
+	CK( cudaGetLastError());
+	return 0;
+}
+
+} /* namespace */
+
+extern "C" {
+
+int rc_dev_init( int device )
+{
+	int n = 0;
+	if( !ck( cudaGetDeviceCount( &n ), "cudaGetDeviceCount" ) || n <= 0 )
+	{
+		if( !D.err[0] ) snprintf( D.err, sizeof( D.err ), "no CUDA device" );
+		return -1;
+	}
+	if( device < 0 || device >= n ) device = 0;
+	CK( cudaSetDevice( device ));
+	cudaDeviceProp prop;
+	CK( cudaGetDeviceProperties( &prop, device ));
+	snprintf( D.name, sizeof( D.name ), "%s (sm_%d%d, %d SMs)", prop.name, prop.major, prop.minor, prop.multiProcessorCount );
+	D.device = device;
+	CK( cudaStreamCreateWithFlags( &D.stream, cudaStreamNonBlocking ));
+	for( auto &e : D.ev ) CK( cudaEventCreate( &e ));
+	CK( cudaFuncSetAttribute( k_scanlines, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)( sizeof( rc_scan_smem_t ) * SCAN_WARPS )));
+	for( int i = 0; i < 256; i++ ) D.h_styles[i] = 256;
+	if( upload( &D.d_styles, D.h_styles, 256 ) != 0 ) return -1;
+	if( dalloc( &D.d_counters, RC_CTR_COUNT ) != 0 ) return -1;
+	CK( cudaMemset( D.d_counters, 0, sizeof( unsigned long long ) * RC_CTR_COUNT ));
+	if( dalloc( &D.d_nlist, 2 ) != 0 ) return -1;
+	D.ready = true;
+	return 0;
+}
+
+void rc_dev_shutdown( void )
+{
+	if( !D.ready ) return;
+	cudaDeviceSynchronize();
+	free_batch();
+	D.ready = false;
+}
+
+const char *rc_dev_last_error( void ) { return D.err; }
+const char *rc_dev_name( void ) { return D.name; }
+uint64_t rc_dev_launch_count( void ) { return D.launches; }
+
+int rc_dev_upload_luts( const uint16_t *colormap, const uint16_t *lightgamma, const int32_t *sintable )
+{
+	if( upload( &D.d_colormap, colormap, 32 * 8192 ) != 0 ) return -1;
+	if( upload( &D.d_lightgamma, lightgamma, 1024 ) != 0 ) return -1;
+	if( upload( &D.d_sintable, sintable, 1280 ) != 0 ) return -1;
+	D.sc.colormap = D.d_colormap; D.sc.lightgamma = D.d_lightgamma; D.sc.sintable = D.d_sintable;
+	return rc_dev_flush_cache();
+}
+
+int rc_dev_upload_textures( const rc_texture_t *tex, int ntex, const uint16_t *texels, size_t ntexels )
+{
+	CK( cudaStreamSynchronize( D.stream ));
+	if( upload( &D.d_textures, tex, (size_t)ntex ) != 0 ) return -1;
+	if( upload( &D.d_texels, texels, ntexels ) != 0 ) return -1;
+	D.h_textures.assign( tex, tex + ntex );
+	D.ntextures = ntex;
+	D.sc.textures = D.d_textures; D.sc.texels = D.d_texels; D.sc.numtextures = ntex;
+	return rc_dev_flush_cache();
+}
+
+int rc_dev_upload_scene( const rc_scene_t *sc, size_t cache_texels )
+{
+	CK( cudaStreamSynchronize( D.stream ));
+	free_batch();
+	rc_scene_t d = *sc;
+	rc_plane_t *planes = (rc_plane_t *)D.d_scene[0]; rc_node_t *nodes = (rc_node_t *)D.d_scene[1];
+	rc_leaf_t *leafs = (rc_leaf_t *)D.d_scene[2]; rc_surface_t *surfaces = (rc_surface_t *)D.d_scene[3];
+	int32_t *marks = (int32_t *)D.d_scene[4], *surfedges = (int32_t *)D.d_scene[5];
+	uint16_t *edges = (uint16_t *)D.d_scene[6]; float *verts = (float *)D.d_scene[7];
+	uint8_t *visdata = (uint8_t *)D.d_scene[8], *lightdata = (uint8_t *)D.d_scene[9];
+	uint16_t *cache = (uint16_t *)D.d_scene[10];
+	if( upload( &planes, sc->planes, (size_t)sc->numplanes ) != 0 ) return -1;
+	if( upload( &nodes, sc->nodes, (size_t)sc->numnodes ) != 0 ) return -1;
+	if( upload( &leafs, sc->leafs, (size_t)sc->numleafs ) != 0 ) return -1;
+	if( upload( &surfaces, sc->surfaces, (size_t)sc->numsurfaces ) != 0 ) return -1;
+	if( upload( &marks, sc->marksurfaces, (size_t)sc->nummarks ) != 0 ) return -1;
+	if( upload( &surfedges, sc->surfedges, (size_t)sc->numsurfedges ) != 0 ) return -1;
+	if( upload( &edges, sc->edges, (size_t)sc->numedges * 2 ) != 0 ) return -1;
+	if( upload( &verts, sc->verts, (size_t)sc->numverts * 3 ) != 0 ) return -1;
+	if( upload( &visdata, sc->visdata, (size_t)sc->visdata_len ) != 0 ) return -1;
+	if( upload( &lightdata, sc->lightdata, (size_t)sc->lightdata_len ) != 0 ) return -1;
+	if( upload( &cache, (const uint16_t *)nullptr, cache_texels ) != 0 ) return -1;
+	D.d_scene[0] = planes; D.d_scene[1] = nodes; D.d_scene[2] = leafs; D.d_scene[3] = surfaces; D.d_scene[4] = marks;
+	D.d_scene[5] = surfedges; D.d_scene[6] = edges; D.d_scene[7] = verts; D.d_scene[8] = visdata; D.d_scene[9] = lightdata;
+	D.d_scene[10] = cache;
+	d.planes = planes; d.nodes = nodes; d.leafs = leafs; d.surfaces = surfaces; d.marksurfaces = marks;
+	d.surfedges = surfedges; d.edges = edges; d.verts = verts; d.visdata = visdata; d.lightdata = lightdata;
+	d.cache = cache;
+	d.textures = D.d_textures; d.texels = D.d_texels; d.numtextures = D.ntextures;
+	d.colormap = D.d_colormap; d.lightgamma = D.d_lightgamma; d.sintable = D.d_sintable;
+	D.sc = d;
+	D.cache_texels = cache_texels;
+	D.h_surfaces.assign( sc->surfaces, sc->surfaces + sc->numsurfaces );
+
+	size_t nslots = (size_t)sc->numsurfaces * 4;
+	if( upload( &D.d_keys, (const rc_cachekey_t *)nullptr, nslots ) != 0 ) return -1;
+	if( upload( &D.d_need, (const uint32_t *)nullptr, nslots / 32 + 2 ) != 0 ) return -1;
+	if( upload( &D.d_list, (const int32_t *)nullptr, nslots ) != 0 ) return -1;
+	return 0;
+}
+
+int rc_dev_update_surface_texnums( const int32_t *texnum, int n )
+{
+	CK( cudaStreamSynchronize( D.stream ));
+	if( n > (int)D.h_surfaces.size()) n = (int)D.h_surfaces.size();
+	for( int i = 0; i < n; i++ ) D.h_surfaces[i].texnum = texnum[i];
+	CK( cudaMemcpy( (void *)D.sc.surfaces, D.h_surfaces.data(), sizeof( rc_surface_t ) * D.h_surfaces.size(), cudaMemcpyHostToDevice ));
+	return 0;
+}
+
+int rc_dev_set_lightstyles( const int32_t *values )
+{
+	if( !memcmp( D.h_styles, values, sizeof( D.h_styles )))
+		return 0;
+	memcpy( D.h_styles, values, sizeof( D.h_styles ));
+	CK( cudaStreamSynchronize( D.stream ));
+	CK( cudaMemcpy( D.d_styles, D.h_styles, sizeof( D.h_styles ), cudaMemcpyHostToDevice ));
+	return 0;
+}
+
+int rc_dev_flush_cache( void )
+{
+	if( D.d_keys && D.sc.numsurfaces )
+	{
+		CK( cudaStreamSynchronize( D.stream ));
+		CK( cudaMemset( D.d_keys, 0, sizeof( rc_cachekey_t ) * (size_t)D.sc.numsurfaces * 4 ));
+	}
+	return 0;
+}
+
+int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, int clear, uint16_t *color_out, int16_t *z_out )
+{
+	if( !D.ready ) { snprintf( D.err, sizeof( D.err ), "device not initialised" ); return -1; }
+	if( !D.sc.numsurfaces || !D.sc.surfaces ) { snprintf( D.err, sizeof( D.err ), "no world uploaded" ); return -1; }
+	if( nviews <= 0 || width <= 0 || height <= 0 || height > 1200 ) { snprintf( D.err, sizeof( D.err ), "bad batch geometry" ); return -1; }
+	if( ensure_batch( nviews, width, height ) != 0 ) return -1;
+	rc_work_t &w = D.w;
+	w.nviews = nviews; w.clear = clear;
+	cudaStream_t st = D.stream;
+	CK( cudaMemcpyAsync( D.d_views, views, sizeof( rc_view_t ) * nviews, cudaMemcpyHostToDevice, st ));
+	size_t px = (size_t)nviews * width * height;
+	if( clear )
+	{
+		/* views that do not cover the whole buffer leave a border the span pass never touches */
+		bool full = true;
+		for( int i = 0; i < nviews && full; i++ )
+			full = views[i].vrect[0] == 0 && views[i].vrect[1] == 0 && views[i].vrect[2] == width && views[i].vrect[3] == height;
+		if( !full )
+		{
+			CK( cudaMemsetAsync( w.color, 0, px * 2, st ));
+			CK( cudaMemsetAsync( w.zbuf, 0, px * 2, st ));
+		}
+	}
+	if( run_stages( false ) != 0 ) return -1;
+	if( color_out ) CK( cudaMemcpyAsync( color_out, w.color, px * 2, cudaMemcpyDeviceToHost, st ));
+	if( z_out ) CK( cudaMemcpyAsync( z_out, w.zbuf, px * 2, cudaMemcpyDeviceToHost, st ));
+	CK( cudaStreamSynchronize( st ));
+	D.have_batch = true;
+	return 0;
+}
+
+int rc_dev_bench_resident( int iters, int rebuild_cache, float *ms_total, float *ms_stage )
+{
+	if( !D.have_batch ) { snprintf( D.err, sizeof( D.err ), "no batch rendered yet" ); return -1; }
+	float tot = 0, stage[4] = { 0, 0, 0, 0 };
+	for( int it = 0; it < iters; it++ )
+	{
+		if( rebuild_cache )
+			CK( cudaMemsetAsync( D.d_keys, 0, sizeof( rc_cachekey_t ) * (size_t)D.sc.numsurfaces * 4, D.stream ));
+		if( run_stages( true ) != 0 ) return -1;
+		CK( cudaStreamSynchronize( D.stream ));
+		float ms;
+		CK( cudaEventElapsedTime( &ms, D.ev[0], D.ev[4] )); tot += ms;
+		for( int s = 0; s < 4; s++ ) { CK( cudaEventElapsedTime( &ms, D.ev[s], D.ev[s + 1] )); stage[s] += ms; }
+	}
+	if( ms_total ) *ms_total = tot / ( iters > 0 ? iters : 1 );
+	if( ms_stage ) for( int s = 0; s < 4; s++ ) ms_stage[s] = stage[s] / ( iters > 0 ? iters : 1 );
+	return 0;
+}
+
+int rc_dev_read_cache_block( int surf, int mip, uint16_t *out, int maxtexels, int *width, int *height, int *valid )
+{
+	if( surf < 0 || surf >= (int)D.h_surfaces.size() || mip < 0 || mip > 3 ) return -1;
+	const rc_surface_t *sf = &D.h_surfaces[surf];
+	int bw = sf->lightextents[0] >> mip, bh = sf->lightextents[1] >> mip;
+	*width = bw; *height = bh; *valid = 0;
+	if( sf->cache_ofs[mip] < 0 ) return 0;
+	rc_cachekey_t k;
+	CK( cudaMemcpy( &k, D.d_keys + surf * 4 + mip, sizeof( k ), cudaMemcpyDeviceToHost ));
+	bool stale = !k.valid || k.texnum != sf->texnum;
+	for( int j = 0; j < 4 && sf->styles[j] != 255 && !stale; j++ )
+		if( k.light[j] != D.h_styles[sf->styles[j]] ) stale = true;
+	*valid = !stale;
+	if( *valid && bw * bh <= maxtexels )
+		CK( cudaMemcpy( out, D.sc.cache + sf->cache_ofs[mip], (size_t)bw * bh * 2, cudaMemcpyDeviceToHost ));
+	return 0;
+}
+
+int rc_dev_read_counters( uint64_t *out, int n )
+{
+	unsigned long long h[RC_CTR_COUNT];
+	CK( cudaMemcpy( h, D.d_counters, sizeof( h ), cudaMemcpyDeviceToHost ));
+	for( int i = 0; i < n && i < RC_CTR_COUNT; i++ ) out[i] = h[i];
+	return 0;
+}
+
+int rc_dev_read_view_surfs( int view, rc_surf_t *out, int max, int *n )
+{
+	if( !D.have_batch || view < 0 || view >= D.w.nviews ) return -1;
+	int32_t nc;
+	CK( cudaMemcpy( &nc, D.w.ncands + view, sizeof( nc ), cudaMemcpyDeviceToHost ));
+	*n = nc;
+	if( nc > max ) nc = max;
+	if( nc > 0 ) CK( cudaMemcpy( out, D.w.surfs + (size_t)view * D.w.max_cands, sizeof( rc_surf_t ) * nc, cudaMemcpyDeviceToHost ));
+	return 0;
+}
+
+int rc_dev_read_view_edges( int view, rc_edge_t *out, int max, int *n )
+{
+	if( !D.have_batch || view < 0 || view >= D.w.nviews ) return -1;
+	int32_t ne;
+	CK( cudaMemcpy( &ne, D.w.nedges + view, sizeof( ne ), cudaMemcpyDeviceToHost ));
+	if( ne > D.w.max_edges ) ne = D.w.max_edges;
+	*n = ne;
+	if( ne > max ) ne = max;
+	if( ne > 0 ) CK( cudaMemcpy( out, D.w.edges + (size_t)view * D.w.max_edges, sizeof( rc_edge_t ) * ne, cudaMemcpyDeviceToHost ));
+	return 0;
+}
+
+} /* extern "C" */

@@ -604,7 +604,7 @@ static void R_NewMap( void )
 	sc.visdata = w->visdata; sc.lightdata = (const uint8_t *)w->lightdata;
 
 	rc.maxdepth = rc_tree_depth( w, w->nodes, 0 );
-	sc.pad0 = rc.maxdepth;
+	sc.maxdepth = rc.maxdepth;
 
 	rc_sync_textures();
 	RC_CHECK_DEV( rc_dev_upload_scene( &sc, cache_texels + 64 ));

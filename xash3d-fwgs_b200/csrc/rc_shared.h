@@ -88,7 +88,7 @@ typedef struct
 {
 	int32_t numplanes, numnodes, numleafs, numsurfaces, nummarks, numsurfedges, numedges, numverts;
 	int32_t visbytes, visdata_len, lightdata_len, numtextures;
-	int32_t numclusters, headnode, pad0, pad1;
+	int32_t numclusters, headnode, maxdepth, pad1; /* maxdepth: BSP tree depth (sizes the walk stack) */
 	const rc_plane_t   *planes;
 	const rc_node_t    *nodes;
 	const rc_leaf_t    *leafs;

@@ -1,0 +1,167 @@
+"""Synthetic scenes + one `Renderer` front end for any renderer plugin behind the headless host.
+
+`Renderer(REF_CUDA_PATH, ...)` drives libref_cuda.so (the product: batched views on the GPU through
+the RefCuda_RenderViews C-ABI entry, include/ref_cuda.h).  `Renderer(REF_SOFT_PATH, ...)` drives the
+unmodified reference ref_soft view by view through GL_RenderFrame (engine/ref_api.h:544) - that is the
+parity oracle and the CPU baseline; only tests, smoke() and bench.py's reference legs construct it.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import functools
+import importlib
+
+import numpy as np
+
+from .hostlib import Host, REF_CUDA_PATH, REF_SOFT_PATH, RF_DRAW_WORLD, calc_fov_y
+
+mapgen = importlib.import_module(__package__ + ".tools.mapgen")
+
+
+class RefViewpass(C.Structure):
+    """common/ref_params.h:97 ref_viewpass_t"""
+
+    _fields_ = [
+        ("viewport", C.c_int * 4),
+        ("vieworigin", C.c_float * 3),
+        ("viewangles", C.c_float * 3),
+        ("viewentity", C.c_int),
+        ("fov_x", C.c_float),
+        ("fov_y", C.c_float),
+        ("flags", C.c_int),
+    ]
+
+
+assert C.sizeof(RefViewpass) == 56
+
+CTR_NAMES = ["views", "pixels", "cands", "surfs", "edges", "spans", "cache_blocks", "cache_texels",
+             "overflow_edges", "overflow_events", "overflow_stack", "overflow_cands"]
+
+
+@functools.lru_cache(maxsize=8)
+def make_map(which: str = "small", ncameras: int = 256, **kw):
+    """Named synthetic worlds of BASELINE.json: tiny (unit tests), small (Map S: C1/C2/C5), large (Map L: C3)."""
+    spec = {"tiny": mapgen.spec_tiny, "small": mapgen.spec_small, "large": mapgen.spec_large}[which](**kw)
+    return mapgen.generate(spec, ncameras=ncameras)
+
+
+class Renderer:
+    def __init__(self, ref_path: str, width: int, height: int, gmap=None, cvars: dict | None = None):
+        self.is_cuda = ref_path == REF_CUDA_PATH or ref_path.endswith("libref_cuda.so") or ref_path.endswith("libref_cuda_emu.so")
+        self.host = Host(ref_path, width, height, cvars)
+        self.width, self.height = width, height
+        L = self.host.lib
+        L.xh_soft_render_views.restype = C.c_double
+        L.xh_soft_render_views.argtypes = [C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        if self.is_cuda:
+            sym = self.host.symbol
+            self._render = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int)(sym("RefCuda_RenderViews"))
+            self._bench = C.CFUNCTYPE(C.c_int, C.c_int, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_float))(sym("RefCuda_BenchResident"))
+            self._readcache = C.CFUNCTYPE(C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int))(sym("RefCuda_ReadSurfaceCache"))
+            self._counters = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int)(sym("RefCuda_GetCounters"))
+            self._launches = C.CFUNCTYPE(C.c_ulonglong)(sym("RefCuda_LaunchCount"))
+            self._devname = C.CFUNCTYPE(C.c_char_p)(sym("RefCuda_DeviceName"))
+        if gmap is not None:
+            self.load_map(gmap)
+
+    def load_map(self, gmap):
+        self.map = gmap
+        self.host.load_map(gmap.bsp, gmap.spec.name)
+        self.host.run_lightstyles()
+
+    # -- time / light styles (engine side)
+    def set_time(self, t):
+        self.host.set_time(t)
+
+    def set_lightstyle(self, i, pattern, time=0.0):
+        self.host.set_lightstyle(i, pattern, time)
+
+    def run_lightstyles(self):
+        self.host.run_lightstyles()
+
+    # -- views
+    def viewpasses(self, cams, fov_x=90.0, flags=RF_DRAW_WORLD, viewport=None):
+        cams = np.asarray(cams, dtype=np.float32).reshape(-1, 6)
+        x, y, w, h = viewport or (0, 0, self.width, self.height)
+        arr = (RefViewpass * len(cams))()
+        fov_y = calc_fov_y(fov_x, w, h)
+        for i, c in enumerate(cams):
+            v = arr[i]
+            v.viewport[:] = [x, y, w, h]
+            v.vieworigin[:] = [float(c[0]), float(c[1]), float(c[2])]
+            v.viewangles[:] = [float(c[3]), float(c[4]), float(c[5])]
+            v.viewentity = 1
+            v.fov_x, v.fov_y, v.flags = fov_x, fov_y, flags
+        return arr
+
+    def render_views(self, cams, fov_x=90.0, clear=True, out=None, flags=RF_DRAW_WORLD, viewport=None, want_z=True):
+        """-> (colour[n,h,w] uint16 pixel_t, z[n,h,w] int16).  `out` = preallocated (colour, z) host arrays
+        (e.g. pinned) to receive the device->host copies."""
+        cams = np.asarray(cams, dtype=np.float32).reshape(-1, 6)
+        n = len(cams)
+        if out is None:
+            color = np.empty((n, self.height, self.width), np.uint16)
+            z = np.empty((n, self.height, self.width), np.int16) if want_z else None
+        else:
+            color, z = out
+        zp = z.ctypes.data if z is not None else None
+        if self.is_cuda:
+            vp = self.viewpasses(cams, fov_x, flags, viewport)
+            rc = self._render(C.addressof(vp), n, color.ctypes.data if color is not None else None, zp, 1 if clear else 0)
+            if rc != 0:
+                raise RuntimeError("RefCuda_RenderViews failed")
+            self.last_seconds = None
+        else:
+            x, y, w, h = viewport or (0, 0, self.width, self.height)
+            cc = np.ascontiguousarray(cams)
+            self.last_seconds = self.host.lib.xh_soft_render_views(cc.ctypes.data, n, fov_x, calc_fov_y(fov_x, w, h), w, h, flags,
+                                                                  1 if clear else 0, color.ctypes.data, zp)
+            if self.last_seconds < 0:
+                raise RuntimeError("not a ref_soft image")
+        return color, z
+
+    def render_resident(self, cams, fov_x=90.0, clear=True):
+        """Render with the results left in HBM (no device->host copy)."""
+        assert self.is_cuda
+        vp = self.viewpasses(cams, fov_x)
+        if self._render(C.addressof(vp), len(vp), None, None, 1 if clear else 0) != 0:
+            raise RuntimeError("RefCuda_RenderViews failed")
+
+    def bench_resident(self, iters, rebuild_cache=False):
+        """CUDA-event ms per iteration of the last batch re-run with inputs resident in HBM: (total, [4 stages])."""
+        tot = C.c_float()
+        st = (C.c_float * 4)()
+        if self._bench(iters, 1 if rebuild_cache else 0, C.byref(tot), st) != 0:
+            raise RuntimeError("RefCuda_BenchResident failed")
+        return tot.value, list(st)
+
+    # -- probes
+    def cache_block(self, surf, mip):
+        if not self.is_cuda:
+            return self.host.soft_cache_block(surf, mip)
+        w, h, valid = C.c_int(), C.c_int(), C.c_int()
+        buf = np.empty(512 * 512, np.uint16)
+        if self._readcache(surf, mip, buf.ctypes.data, buf.size, C.byref(w), C.byref(h), C.byref(valid)) != 0:
+            return None
+        if not valid.value:
+            return None
+        return buf[: w.value * h.value].reshape(h.value, w.value).copy()
+
+    def counters(self) -> dict:
+        a = np.zeros(32, np.uint64)
+        self._counters(a.ctypes.data, 32)
+        return dict(zip(CTR_NAMES, [int(x) for x in a[: len(CTR_NAMES)]]))
+
+    def launch_count(self) -> int:
+        return int(self._launches())
+
+    def device_name(self) -> str:
+        return self._devname().decode()
+
+
+def compare_frames(a_col, a_z, b_col, b_z):
+    """Fraction of identical pixels (colour, z) and whether every differing pixel sits within one pixel of
+    a place where the reference image changes surface (a span boundary), per BASELINE.json's tolerance."""
+    same_c = float((a_col == b_col).mean())
+    same_z = float((a_z == b_z).mean()) if a_z is not None and b_z is not None else 1.0
+    return same_c, same_z
