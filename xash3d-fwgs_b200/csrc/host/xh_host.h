@@ -67,7 +67,7 @@ XH_EXPORT const char *xh_last_error( void );
 XH_EXPORT const void *xh_soft_cache_block( int surf, int mip, int *width, int *height );
 /* oracle-only driver loop: n cameras (x y z pitch yaw roll) through ref_soft's GL_RenderFrame, buffers copied out
  * per view; returns the seconds spent inside GL_RenderFrame (xh_probe_soft.c) */
-XH_EXPORT double xh_soft_render_views( const float *cams, int n, float fov_x, float fov_y, int w, int h, int flags, int clear,
+XH_EXPORT double xh_soft_render_views( const float *cams, int n, float fov_x, float fov_y, int x, int y, int w, int h, int flags, int clear,
 	unsigned short *color_out, short *z_out );
 
 #ifdef __cplusplus

@@ -20,7 +20,9 @@ const void *xh_soft_cache_block( int surf, int mip, int *width, int *height )
 	if( !c )
 		return NULL;
 	if( width ) *width = (int)c->width;
-	if( height ) *height = (int)c->height;
+	/* surfcache_t.height is a debug field counted in bytes per row (r_surf.c:896); the block D_CacheSurface
+	 * fills is lightextents[1] >> mip rows (r_surf.c:1126) */
+	if( height ) *height = m->surfaces[surf].info->lightextents[1] >> mip;
 	return c->data;
 }
 
@@ -33,7 +35,7 @@ const void *xh_soft_cache_block( int surf, int mip, int *width, int *height )
  */
 #include <time.h>
 
-double xh_soft_render_views( const float *cams, int n, float fov_x, float fov_y, int w, int h, int flags, int clear,
+double xh_soft_render_views( const float *cams, int n, float fov_x, float fov_y, int x, int y, int w, int h, int flags, int clear,
 	unsigned short *color_out, short *z_out )
 {
 	viddef_t *pvid = (viddef_t *)xh_ref_symbol( "vid" );
@@ -54,7 +56,7 @@ double xh_soft_render_views( const float *cams, int n, float fov_x, float fov_y,
 		}
 		*oldcluster = -2;
 		clock_gettime( CLOCK_MONOTONIC, &t0 );
-		xh_render_view( c, c + 3, fov_x, fov_y, 0, 0, w, h, flags );
+		xh_render_view( c, c + 3, fov_x, fov_y, x, y, w, h, flags );
 		clock_gettime( CLOCK_MONOTONIC, &t1 );
 		total += ( t1.tv_sec - t0.tv_sec ) + 1e-9 * ( t1.tv_nsec - t0.tv_nsec );
 		if( color_out ) memcpy( color_out + px * i, pvid->buffer, px * sizeof( pixel_t ));

@@ -34,6 +34,7 @@ def calc_fov_y(fov_x: float, width: float, height: float) -> float:
 
 class Host:
     _copies = 0
+    _loaded_refs: set = set()
 
     def __init__(self, ref_path: str, width: int, height: int, cvars: dict | None = None):
         if not os.path.exists(HOST_LIB_PATH):
@@ -74,7 +75,18 @@ class Host:
         self.ref_path = ref_path
         for k, v in (cvars or {}).items():
             L.xh_cvar_set(k.encode(), str(v).encode())
-        rc = L.xh_init(ref_path.encode(), width, height)
+        # renderers keep process-global state: a second instance of the same plugin in this process gets a
+        # private image of it too (the first one is loaded in place, from the tree)
+        load_path, tmp_ref = ref_path, None
+        if os.path.realpath(ref_path) in Host._loaded_refs:
+            t = tempfile.NamedTemporaryFile(prefix=f"xashref{Host._copies}_", suffix=".so", delete=False)
+            t.close()
+            shutil.copyfile(ref_path, t.name)
+            load_path = tmp_ref = t.name
+        Host._loaded_refs.add(os.path.realpath(ref_path))
+        rc = L.xh_init(load_path.encode(), width, height)
+        if tmp_ref:
+            os.unlink(tmp_ref)
         if rc != 0:
             raise RuntimeError(f"xh_init({ref_path}) failed: {rc} {L.xh_last_error().decode()}")
         self._map = None

@@ -52,7 +52,7 @@ class Renderer:
         self.width, self.height = width, height
         L = self.host.lib
         L.xh_soft_render_views.restype = C.c_double
-        L.xh_soft_render_views.argtypes = [C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        L.xh_soft_render_views.argtypes = [C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         if self.is_cuda:
             sym = self.host.symbol
             self._render = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int)(sym("RefCuda_RenderViews"))
@@ -114,7 +114,7 @@ class Renderer:
         else:
             x, y, w, h = viewport or (0, 0, self.width, self.height)
             cc = np.ascontiguousarray(cams)
-            self.last_seconds = self.host.lib.xh_soft_render_views(cc.ctypes.data, n, fov_x, calc_fov_y(fov_x, w, h), w, h, flags,
+            self.last_seconds = self.host.lib.xh_soft_render_views(cc.ctypes.data, n, fov_x, calc_fov_y(fov_x, w, h), x, y, w, h, flags,
                                                                   1 if clear else 0, color.ctypes.data, zp)
             if self.last_seconds < 0:
                 raise RuntimeError("not a ref_soft image")
