@@ -1,0 +1,351 @@
+#!/usr/bin/env python
+"""bench.py - rendered Mpixel/s of batched camera views (BASELINE.json metric), ref/cuda vs ref_soft.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]            # our arm (libref_cuda.so on the GPU)
+    python bench.py --impl reference [--gpus N] ...                # the reference's CPU path (unmodified ref_soft)
+
+A step = one batch of `--views` camera views (default 256 at 320x240 on the synthetic Map S: BASELINE.json
+configs[1]) through the whole frame path.  N > 1: one rank per GPU (torchrun), every rank renders its own
+256-view slice of the camera list (weak scaling, no data-path collective; NCCL only gathers the timing
+and the counters).
+
+  value  = whole-job Mpixel/s with the batch's inputs resident in HBM (CUDA events around the device stages,
+           L2 flushed between steps, max over ranks)
+  e2e    = the same through the plugin's public C-ABI call RefCuda_RenderViews with HOST buffers: view
+           descriptors go host->device and the colour frames come back device->host (pinned) every step
+  roofline = the span kernel (k_scanlines): 6 algorithmic bytes per pixel / its CUDA-event time vs the
+           measured HBM copy bandwidth (MEASURED_PEAKS.json)
+  cpu_baseline = the oracle (unmodified ref_soft, oracle/_ref) timed on one host core on a bounded sample
+"""
+from __future__ import annotations
+
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "rendered Mpixel/s (batched views)"
+UNIT = "Mpixel/s"
+BYTES_PER_PIXEL = 6  # 2 B colour write + 2 B z write + 2 B cache texel read
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
+    ap.add_argument("--views", type=int, default=256, help="views per GPU per step")
+    ap.add_argument("--width", type=int, default=320)
+    ap.add_argument("--height", type=int, default=240)
+    ap.add_argument("--map", default="small", choices=["tiny", "small", "large"])
+    ap.add_argument("--cpu-seconds", type=float, default=10.0, help="budget of the cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def workload(args, world):
+    return {
+        "workload": f"{args.views} batched camera views/GPU at {args.width}x{args.height}, synthetic BSP30 Map "
+                    f"{'S (~1.7k faces)' if args.map == 'small' else args.map}, static lightmaps (BASELINE.json configs[1])",
+        "views_per_gpu": args.views, "width": args.width, "height": args.height, "map": args.map,
+        "sharding": f"views x{world}, scene replicated, no data-path collective",
+        "l2": "flushed with a 256 MB write between timed steps",
+    }
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def measured_traffic():
+    """dram bytes per launch of the span kernel from the committed ncu capture, if one exists."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p)).get("k_scanlines_dram_bytes_per_launch")
+        except Exception:
+            return None
+    return None
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index=0):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(index)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = float(r[1])
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# the reference's CPU implementation (oracle/_ref/libref_soft.so under the headless host)
+
+def _soft_worker(conn, args_d, lo, hi, ncams):
+    """one ref_soft instance (all-globals, single-threaded) per process, one process per host core"""
+    try:
+        try:
+            os.sched_setaffinity(0, {args_d["cpu"]})
+        except Exception:
+            pass
+        pkg = importlib.import_module("xash3d-fwgs_b200")
+        scene = importlib.import_module("xash3d-fwgs_b200.scene")
+        m = scene.make_map(args_d["map"], ncameras=ncams)
+        r = scene.Renderer(pkg.REF_SOFT_PATH, args_d["width"], args_d["height"], m)
+        cams = m.cameras[lo:hi]
+        out = (np.empty((len(cams), args_d["height"], args_d["width"]), np.uint16), np.empty((len(cams), args_d["height"], args_d["width"]), np.int16))
+        conn.send("ready")
+        while True:
+            cmd = conn.recv()
+            if cmd == "quit":
+                break
+            t0 = time.perf_counter()
+            r.render_views(cams, out=out)
+            conn.send((time.perf_counter() - t0, r.last_seconds))
+    except Exception as e:  # pragma: no cover
+        conn.send(("error", repr(e)))
+
+
+class SoftPool:
+    def __init__(self, args, ncores):
+        import multiprocessing as mp
+
+        ctx = mp.get_context("spawn")
+        self.n = min(ncores, args.views)
+        cpus = sorted(os.sched_getaffinity(0))
+        bounds = np.linspace(0, args.views, self.n + 1).astype(int)
+        self.procs = []
+        for i in range(self.n):
+            a, b = ctx.Pipe()
+            d = {"map": args.map, "width": args.width, "height": args.height, "cpu": cpus[i % len(cpus)]}
+            p = ctx.Process(target=_soft_worker, args=(b, d, int(bounds[i]), int(bounds[i + 1]), args.views), daemon=True)
+            p.start()
+            self.procs.append((p, a))
+        for _, a in self.procs:
+            msg = a.recv()
+            if msg != "ready":
+                raise RuntimeError(f"ref_soft worker failed: {msg}")
+
+    def step(self):
+        """all workers render their slice of the batch once; -> (wall seconds, max seconds inside R_RenderFrame)"""
+        t0 = time.perf_counter()
+        for _, a in self.procs:
+            a.send("go")
+        res = [a.recv() for _, a in self.procs]
+        wall = time.perf_counter() - t0
+        if any(r[0] == "error" for r in res):
+            raise RuntimeError(str(res))
+        return wall, max(r[1] for r in res)
+
+    def close(self):
+        for p, a in self.procs:
+            try:
+                a.send("quit")
+            except Exception:
+                pass
+        for p, _ in self.procs:
+            p.join(timeout=5)
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    ncores = len(os.sched_getaffinity(0))
+    pool = SoftPool(args, ncores)
+    for _ in range(args.warmup):
+        pool.step()
+    walls, inner = [], []
+    for _ in range(args.steps):
+        w, i = pool.step()
+        walls.append(w)
+        inner.append(i)
+    pool.close()
+    px = args.views * args.width * args.height
+    # time of a step = the slowest process's time inside GL_RenderFrame (R_RenderFrame only)
+    ms = 1e3 * float(np.mean(inner))
+    val = px / (ms * 1e3)
+    sample = f"{args.steps} passes of the {args.views}-view batch split over {pool.n} processes (one ref_soft per core)"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32/f32 (16-bit pixel_t)",
+        "data": "synthetic", "config": workload(args, 1),
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": pool.n, "kind": "reference", "sample": sample,
+                         "wall_ms_per_step_incl_ipc": 1e3 * float(np.mean(walls))},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def cpu_baseline_one_core(args):
+    """the oracle on ONE host core, a bounded sample of the same workload (reported baseline, not the target)"""
+    pkg = importlib.import_module("xash3d-fwgs_b200")
+    scene = importlib.import_module("xash3d-fwgs_b200.scene")
+    m = scene.make_map(args.map, ncameras=args.views)
+    r = scene.Renderer(pkg.REF_SOFT_PATH, args.width, args.height, m)
+    cams = m.cameras[: args.views]
+    out = (np.empty((len(cams), args.height, args.width), np.uint16), np.empty((len(cams), args.height, args.width), np.int16))
+    r.render_views(cams, out=out)  # warm: fills the surface cache
+    secs, passes, t0 = 0.0, 0, time.perf_counter()
+    while time.perf_counter() - t0 < args.cpu_seconds and passes < 1000:
+        r.render_views(cams, out=out)
+        secs += r.last_seconds
+        passes += 1
+    px = passes * len(cams) * args.width * args.height
+    return {"value": px / secs / 1e6, "unit": UNIT, "cores": 1, "kind": "reference",
+            "sample": f"{passes} passes of the {len(cams)}-view batch ({secs:.1f} s inside GL_RenderFrame), warm surface cache, gcc -O2"}
+
+
+# ------------------------------------------------------------------------------------------------
+# our arm: libref_cuda.so
+
+def run_cuda(args):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device - ref/cuda has no CPU path (use --impl reference for ref_soft)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def allmax(x):
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    pkg = importlib.import_module("xash3d-fwgs_b200")
+    scene = importlib.import_module("xash3d-fwgs_b200.scene")
+    shard = importlib.import_module("xash3d-fwgs_b200.shard")
+    m = scene.make_map(args.map, ncameras=args.views * world)
+    lo, hi = shard.view_range(args.views * world, rank, world)  # this rank's slice of the global camera list
+    cams = m.cameras[lo:hi]
+    r = scene.Renderer(pkg.REF_CUDA_PATH, args.width, args.height, m, cvars={"cu_device": local})
+    n, w, h = len(cams), args.width, args.height
+    px = n * w * h
+
+    # pinned host landing zone for the e2e leg (torch only provides the pinned allocation)
+    pin = torch.empty((n, h, w), dtype=torch.int16).pin_memory()
+    vp = r.viewpasses(cams)
+    r.render_prepared(vp, pin.data_ptr(), None)  # uploads the batch, builds the surface cache blocks it needs
+    ctr0 = r.counters()
+    overflow = {k: v for k, v in ctr0.items() if k.startswith("overflow") and v}
+    if overflow:
+        raise SystemExit(f"bench.py: capacity overflow {overflow} - numbers would be invalid")
+
+    # -- value: device stages, inputs resident, CUDA events inside the plugin, L2 flushed between steps
+    r.bench_resident(max(args.warmup, 3), flush_l2=True)
+    sampler = ClockSampler(local) if rank == 0 else None
+    barrier()
+    l0 = r.launch_count()
+    ms, stages = r.bench_resident(args.steps, flush_l2=True)
+    launches = r.launch_count() - l0
+    barrier()
+    ms_step = allmax(ms)
+    ms_scan = allmax(stages[3])
+
+    # -- e2e: the public C-ABI call with host buffers (H2D view descriptors, D2H colour frames), wall clock
+    for _ in range(max(args.warmup, 3)):
+        r.render_prepared(vp, pin.data_ptr(), None)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        r.render_prepared(vp, pin.data_ptr(), None)
+    torch.cuda.synchronize()
+    e2e_s = allmax((time.perf_counter() - t0) / args.steps)
+    barrier()
+    clocks = sampler.stop() if sampler else None
+
+    # counters of the last batch, summed over ranks (the only collective: < 1 KiB, off the data path)
+    names = list(ctr0.keys())
+    ctr = torch.tensor([float(r.counters()[k]) for k in names], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(ctr, op=dist.ReduceOp.SUM)
+    counters = {k: int(v) for k, v in zip(names, ctr.tolist())}
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        total_px = px * world
+        achieved = BYTES_PER_PIXEL * px / (ms_scan * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": total_px / (ms_step * 1e3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "int32/f32 (16-bit pixel_t)", "data": "synthetic", "config": workload(args, world),
+            "frames_per_s": n * world / (ms_step * 1e-3),
+            "stage_ms": {"vis_walk": stages[0], "faces_edges": stages[1], "surface_cache": stages[2], "scanlines": stages[3]},
+            "e2e": {"value": total_px / e2e_s / 1e6, "unit": UNIT, "h2d_bytes_per_step": n * 56, "d2h_bytes_per_step": px * 2,
+                    "ms_per_step": e2e_s * 1e3, "note": "RefCuda_RenderViews: ref_viewpass_t array in, colour frames out to pinned host memory"},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "kernel": "k_scanlines", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": measured_traffic(), "algorithmic_bytes_per_launch": BYTES_PER_PIXEL * px, "peak_source": peak_src,
+                         "kernel_ms": ms_scan},
+            "clocks": clocks, "counters": counters, "device": r.device_name(),
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline_one_core(args)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_cuda(a)

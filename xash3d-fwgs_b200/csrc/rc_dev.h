@@ -41,7 +41,9 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 
 /* re-run the device stages of the last rc_dev_render batch (inputs resident in HBM) 'iters' times and
  * report CUDA-event milliseconds: total and per stage (vis+walk, faces, cache, scan) */
-int rc_dev_bench_resident( int iters, int rebuild_cache, float *ms_total, float *ms_stage /* [4] */ );
+#define RC_BENCH_REBUILD_CACHE 1 /* invalidate every cache block before each iteration (config C3 behaviour) */
+#define RC_BENCH_FLUSH_L2      2 /* write 256 MB between iterations, outside the timed region */
+int rc_dev_bench_resident( int iters, int flags, float *ms_total, float *ms_stage /* [4] */ );
 
 /* probes for the parity tests */
 int rc_dev_read_cache_block( int surf, int mip, uint16_t *out, int maxtexels, int *width, int *height, int *valid );

@@ -537,6 +537,7 @@ struct Dev
 	rc_view_t *d_views = nullptr;
 	void *d_work[20] = {};
 	bool have_batch = false;
+	void *d_flush = nullptr;
 } D;
 
 bool ck( cudaError_t e, const char *what )
@@ -820,13 +821,18 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 	return 0;
 }
 
-int rc_dev_bench_resident( int iters, int rebuild_cache, float *ms_total, float *ms_stage )
+int rc_dev_bench_resident( int iters, int flags, float *ms_total, float *ms_stage )
 {
 	if( !D.have_batch ) { snprintf( D.err, sizeof( D.err ), "no batch rendered yet" ); return -1; }
 	float tot = 0, stage[4] = { 0, 0, 0, 0 };
+	const size_t flush_bytes = (size_t)256 << 20; /* > 126 MB of L2 */
+	if(( flags & RC_BENCH_FLUSH_L2 ) && !D.d_flush )
+		CK( cudaMalloc( &D.d_flush, flush_bytes ));
 	for( int it = 0; it < iters; it++ )
 	{
-		if( rebuild_cache )
+		if( flags & RC_BENCH_FLUSH_L2 ) /* untimed: the events bracket the stages only */
+			CK( cudaMemsetAsync( D.d_flush, it & 0xFF, flush_bytes, D.stream ));
+		if( flags & RC_BENCH_REBUILD_CACHE )
 			CK( cudaMemsetAsync( D.d_keys, 0, sizeof( rc_cachekey_t ) * (size_t)D.sc.numsurfaces * 4, D.stream ));
 		if( run_stages( true ) != 0 ) return -1;
 		CK( cudaStreamSynchronize( D.stream ));

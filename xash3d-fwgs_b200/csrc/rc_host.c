@@ -878,9 +878,9 @@ int RefCuda_RenderViews( const ref_viewpass_t *views, int nviews, unsigned short
 	return r;
 }
 
-int RefCuda_BenchResident( int iters, int rebuild_cache, float *ms_total, float *ms_stage )
+int RefCuda_BenchResident( int iters, int flags, float *ms_total, float *ms_stage )
 {
-	return rc_dev_bench_resident( iters, rebuild_cache, ms_total, ms_stage );
+	return rc_dev_bench_resident( iters, flags, ms_total, ms_stage );
 }
 
 int RefCuda_ReadSurfaceCache( int surf, int mip, unsigned short *out, int maxtexels, int *width, int *height, int *valid )

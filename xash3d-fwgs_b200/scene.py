@@ -127,11 +127,16 @@ class Renderer:
         if self._render(C.addressof(vp), len(vp), None, None, 1 if clear else 0) != 0:
             raise RuntimeError("RefCuda_RenderViews failed")
 
-    def bench_resident(self, iters, rebuild_cache=False):
+    def render_prepared(self, vp, color_ptr, z_ptr, clear=True):
+        """RefCuda_RenderViews on a prebuilt ref_viewpass_t array and raw host pointers (bench e2e leg)."""
+        if self._render(C.addressof(vp), len(vp), color_ptr, z_ptr, 1 if clear else 0) != 0:
+            raise RuntimeError("RefCuda_RenderViews failed")
+
+    def bench_resident(self, iters, rebuild_cache=False, flush_l2=False):
         """CUDA-event ms per iteration of the last batch re-run with inputs resident in HBM: (total, [4 stages])."""
         tot = C.c_float()
         st = (C.c_float * 4)()
-        if self._bench(iters, 1 if rebuild_cache else 0, C.byref(tot), st) != 0:
+        if self._bench(iters, (1 if rebuild_cache else 0) | (2 if flush_l2 else 0), C.byref(tot), st) != 0:
             raise RuntimeError("RefCuda_BenchResident failed")
         return tot.value, list(st)
 
