@@ -188,14 +188,19 @@ def test_no_clear_keeps_previous_pixels(cu_small, so_small):
     assert np.array_equal(a, b)
 
 
-def test_partial_viewport(cu_small, so_small):
-    cu, m = cu_small
-    so, _ = so_small
+def test_partial_viewport(pkg, scene):
+    """A view smaller than the screen buffer.  The oracle gets a fresh instance: R_BeginEdgeFrame only clears
+    newedges[] inside the current vrect while R_ScanEdges starts at scanline 0 (r_edge.c:81-118,627), so ref_soft
+    itself walks stale edge lists (and crashes) when the viewport shrinks after a full-screen frame."""
+    m = scene.make_map("tiny", ncameras=16)
+    cu = scene.Renderer(pkg.REF_CUDA_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    cu.render_views(m.cameras[:4])  # ours may follow a full-screen batch
     vp = (40, 30, 200, 150)
     cc, cz = cu.render_views(m.cameras[:4], viewport=vp)
     rc, rz = so.render_views(m.cameras[:4], viewport=vp)
     assert (cc == rc).mean() >= TOL and (cz == rz).mean() >= TOL
-    assert not cc[:, :30].any() and not cc[:, :, :40].any()
+    assert not cc[:, :30].any() and not cc[:, :, :40].any() and not cc[:, 180:].any() and not cc[:, :, 240:].any()
 
 
 def test_full_c2_batch_properties(cu_small, so_small):
