@@ -197,6 +197,22 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 			int32_t ovf = 0;
 			int ns = rc_generate_spans( ev.data(), (int)ev.size(), head_iu, tail_u, stk.data(), cnt.data(), ncands + 1, neg.data(), 64,
 				spans.data(), (int)spans.size(), &ovf );
+			{
+				/* the bit-set formulation the scanline kernel uses must give the same spans */
+				std::vector<uint32_t> bits(( ncands + 32 ) / 32 + 1, 0u );
+				std::vector<rc_span_t> spans2( spans.size());
+				int32_t exc[32], ovf2 = 0;
+				int ns2 = rc_generate_spans_bits( ev.data(), (int)ev.size(), head_iu, tail_u, bits.data(), (int)bits.size(), exc, 16,
+					spans2.data(), (int)spans2.size(), &ovf2 );
+				bool same = ns2 == ns && ovf2 == ovf;
+				for( int k = 0; same && k < ns; k++ )
+					same = spans[k].u == spans2[k].u && spans[k].count == spans2[k].count && spans[k].surf == spans2[k].surf;
+				if( !same )
+				{
+					fprintf( stderr, "rc_emu: span replay mismatch view %d line %d (%d vs %d spans)\n", vi, y, ns, ns2 );
+					E.counters[RC_CTR_OVERFLOW_CANDS]++;
+				}
+			}
 			if( ovf ) E.counters[RC_CTR_OVERFLOW_EVENTS]++;
 			E.counters[RC_CTR_SPANS] += ns;
 			if( const char *dbg = getenv( "RC_EMU_DEBUG" ))

@@ -56,7 +56,7 @@ def test_kernels_are_the_thing_that_runs(cu_small):
     cu, m = cu_small
     before = cu.launch_count()
     cu.render_views(m.cameras[:4])
-    assert cu.launch_count() - before >= 7
+    assert cu.launch_count() - before >= 4
     assert "B200" in cu.device_name() or "sm_" in cu.device_name()
 
 

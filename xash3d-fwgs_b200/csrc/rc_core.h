@@ -583,7 +583,7 @@ RC_HD void rc_render_face( const rc_scene_t *sc, const rc_view_t *vw, const rc_c
 /* A4: span generation for one scanline (ref/soft/r_edge.c:360-583)                             */
 
 typedef struct { int32_t u; uint32_t surfs; } rc_event_t; /* an active edge at this scanline */
-typedef struct { int32_t u, count, surf; } rc_span_t;     /* surf: 0 = background, else candidate index + 1 */
+typedef struct { int32_t surf; int16_t u, count; } rc_span_t;  /* 8 B; surf: 0 = background, else candidate index + 1 */
 
 /* edge->u after (y - v) executions of "edge->u += edge->u_step" (R_StepActiveU, r_edge.c:187): int32 wraparound */
 RC_HD int32_t rc_edge_u_at( const rc_edge_t *e, int32_t y )
@@ -620,7 +620,7 @@ RC_HD int32_t rc_generate_spans( const rc_event_t *ev, int32_t nev, int32_t head
 	int32_t top = 0, top_last_u = head_iu; /* surfaces[1].last_u = edge_head_u_shift20 */
 
 #define RC_EMIT_SPAN( SURF, LAST, IU ) \
-	if(( IU ) > ( LAST )) { if( nspans < maxspans ) { spans[nspans].u = ( LAST ); spans[nspans].count = ( IU ) - ( LAST ); spans[nspans].surf = ( SURF ); nspans++; } else *overflow = 1; }
+	if(( IU ) > ( LAST )) { if( nspans < maxspans ) { spans[nspans].u = (int16_t)( LAST ); spans[nspans].count = (int16_t)(( IU ) - ( LAST )); spans[nspans].surf = ( SURF ); nspans++; } else *overflow = 1; }
 
 	for( int32_t e = 0; e < nev; e++ )
 	{
@@ -691,6 +691,112 @@ RC_HD int32_t rc_generate_spans( const rc_event_t *ev, int32_t nev, int32_t head
 	return nspans;
 }
 
+/*
+ * The same replay with the surface stack kept as a bit set.  Only two things about the key-ordered stack
+ * ever reach the output: which surfaces are on it (spanstate >= 1) and which of them has the smallest key
+ * (world keys are unique and equal the candidate order, so "smallest key" = lowest set bit).  A surface's
+ * spanstate is 0 or 1 except on degenerate scanlines (inverted spans, a surface entered twice); those few
+ * live in the exception list exc[] = {surf, spanstate} with spanstate outside {0, 1}.
+ * bits: (maxsurf + 32) / 32 words, zeroed by the caller.  Returns the number of spans written.
+ */
+RC_HD int32_t rc_generate_spans_bits( const rc_event_t *ev, int32_t nev, int32_t head_iu, int32_t tail_u,
+	uint32_t *bits, int32_t nwords, int32_t *exc, int32_t exccap, rc_span_t *spans, int32_t maxspans, int32_t *overflow )
+{
+	int32_t nexc = 0, nspans = 0;
+	int32_t top = 0, top_last_u = head_iu; /* 0 = background (surfaces[1], key 0x7FFFFFFF) */
+
+#define RC_EMIT_SPAN( SURF, LAST, IU ) \
+	if(( IU ) > ( LAST )) { if( nspans < maxspans ) { spans[nspans].u = (int16_t)( LAST ); spans[nspans].count = (int16_t)(( IU ) - ( LAST )); spans[nspans].surf = ( SURF ); nspans++; } else *overflow = 1; }
+
+	for( int32_t e = 0; e < nev; e++ )
+	{
+		const int32_t u = ev[e].u;
+		const uint32_t both = ev[e].surfs;
+		if( u > tail_u )
+			break;
+		const int32_t iu = u >> 20;
+		const int32_t trail = (int32_t)( both & 0xFFFF ), lead = (int32_t)( both >> 16 );
+
+		if( trail )
+		{
+			int32_t x = -1;
+			for( int32_t i = 0; i < nexc; i++ ) if( exc[2 * i] == trail ) { x = i; break; }
+			if( x >= 0 )
+			{
+				/* spanstate 2 -> 1 returns to the plain representation (bit stays set); others just count down */
+				if( --exc[2 * x + 1] == 1 ) { exc[2 * x] = exc[2 * ( nexc - 1 )]; exc[2 * x + 1] = exc[2 * ( nexc - 1 ) + 1]; nexc--; }
+			}
+			else if(( bits[trail >> 5] >> ( trail & 31 )) & 1 )
+			{
+				/* R_TrailingEdge: --spanstate == 0 -> leave the stack */
+				bits[trail >> 5] &= ~( 1u << ( trail & 31 ));
+				if( trail == top )
+				{
+					RC_EMIT_SPAN( trail, top_last_u, iu )
+					top_last_u = iu;
+					/* the next surface on the stack: lowest set bit above the old top */
+					int32_t wi = trail >> 5;
+					uint32_t wv = bits[wi] & ~(( 2u << ( trail & 31 )) - 1u );
+					top = 0;
+					for( ;; )
+					{
+						if( wv )
+						{
+#if defined( __CUDA_ARCH__ )
+							top = ( wi << 5 ) + ( __ffs( (int)wv ) - 1 );
+#else
+							top = ( wi << 5 ) + __builtin_ctz( wv );
+#endif
+							break;
+						}
+						if( ++wi >= nwords ) break;
+						wv = bits[wi];
+					}
+				}
+			}
+			else
+			{
+				/* inverted span: spanstate goes negative */
+				if( nexc < exccap ) { exc[2 * nexc] = trail; exc[2 * nexc + 1] = -1; nexc++; }
+				else *overflow = 1;
+			}
+		}
+		if( lead )
+		{
+			int32_t x = -1;
+			for( int32_t i = 0; i < nexc; i++ ) if( exc[2 * i] == lead ) { x = i; break; }
+			if( x >= 0 )
+			{
+				/* spanstate -1 -> 0 returns to the plain representation (bit stays clear) */
+				if( ++exc[2 * x + 1] == 0 ) { exc[2 * x] = exc[2 * ( nexc - 1 )]; exc[2 * x + 1] = exc[2 * ( nexc - 1 ) + 1]; nexc--; }
+			}
+			else if(( bits[lead >> 5] >> ( lead & 31 )) & 1 )
+			{
+				/* already on the stack: spanstate 2 */
+				if( nexc < exccap ) { exc[2 * nexc] = lead; exc[2 * nexc + 1] = 2; nexc++; }
+				else *overflow = 1;
+			}
+			else
+			{
+				/* R_LeadingEdge: ++spanstate == 1 -> enter the stack; in front of everything -> new top */
+				bits[lead >> 5] |= 1u << ( lead & 31 );
+				if( !top || lead < top )
+				{
+					RC_EMIT_SPAN( top, top_last_u, iu )
+					top_last_u = iu;
+					top = lead;
+				}
+			}
+		}
+	}
+	{
+		int32_t iu = tail_u >> 20;
+		RC_EMIT_SPAN( top, top_last_u, iu )
+	}
+#undef RC_EMIT_SPAN
+	return nspans;
+}
+
 /* ------------------------------------------------------------------------------------------ */
 /* A9/A10/A11: span drawing split into chunk set-up (float, once per 8 or 16 pixels) and the    */
 /* per-pixel integer part (ref/soft/r_scan.c:89-221,528-668,1309-1357)                          */
@@ -724,39 +830,29 @@ RC_HD int32_t rc_clamp_st( int32_t x, int32_t hi, int32_t lo )
 	return x;
 }
 
-/*
- * State of D_DrawSpans16 / Turbulent8 at the start of chunk j of a span (u, v, count).  The reference
- * walks the chunks sequentially accumulating sdivz/tdivz/zi in float; chunk j repeats those j additions
- * so that chunks can be set up independently (one lane each) with bit-identical results.
- */
-RC_HD void rc_chunk_setup( const rc_view_t *vw, const rc_surf_t *sf, int32_t sky_color, int32_t u, int32_t v, int32_t count, int32_t j, rc_chunk_t *c )
+/* D_DrawZSpans (r_scan.c:1309): 1/z of the span's first pixel as a 1.31 integer + the per-pixel step; later
+ * pixels are integer steps from there (int32 wraparound) */
+RC_HD void rc_span_z0( const rc_surf_t *sf, int32_t u, int32_t v, int32_t *izi0, int32_t *izistep )
 {
-	int32_t kind = rc_span_kind( sf );
+	float du = (float)u, dv = (float)v;
+	float zi = sf->d_ziorigin + dv * sf->d_zistepv + du * sf->d_zistepu;
+	*izistep = rc_f2i( sf->d_zistepu * (float)0x8000 * (float)0x10000 );
+	*izi0 = rc_f2i( zi * (float)0x8000 * (float)0x10000 );
+}
+
+/* texture coordinates (16.16) of the first pixel of chunk j of the span (u, v, count) and their per-pixel step */
+RC_HD void rc_chunk_st( const rc_surf_t *sf, int32_t kind, int32_t u, int32_t v, int32_t count, int32_t j,
+	int32_t *ps, int32_t *pt, int32_t *psstep, int32_t *ptstep )
+{
 	int32_t px = kind == RC_KIND_TURB ? 16 : 8;
 	float du = (float)u, dv = (float)v;
-
-	/* D_DrawZSpans: closed form per pixel */
 	float zi = sf->d_ziorigin + dv * sf->d_zistepv + du * sf->d_zistepu;
-	int32_t izistep = rc_f2i( sf->d_zistepu * (float)0x8000 * (float)0x10000 );
-	int32_t izi0 = rc_f2i( zi * (float)0x8000 * (float)0x10000 );
-	c->izistep = izistep;
-	c->izi = (int32_t)((uint32_t)izi0 + (uint32_t)( j * px ) * (uint32_t)izistep );
-	c->u0 = u + j * px;
-	c->kind = kind;
-	c->base = sf->cache_ofs;
-	c->width = sf->cachewidth;
-	c->s = c->t = c->sstep = c->tstep = 0;
-	if( kind == RC_KIND_SKY )
-	{
-		c->base = sky_color;
-		return;
-	}
-
 	float sdivz = sf->d_sdivzorigin + dv * sf->d_sdivzstepv + du * sf->d_sdivzstepu;
 	float tdivz = sf->d_tdivzorigin + dv * sf->d_tdivzstepv + du * sf->d_tdivzstepu;
 	float fpx = (float)px;
 	float sdivzstep = sf->d_sdivzstepu * fpx, tdivzstep = sf->d_tdivzstepu * fpx, zistep = sf->d_zistepu * fpx;
 	int32_t nchunks = rc_span_nchunks( kind, count );
+	int32_t sstep = 0, tstep = 0;
 
 	/* s/t of the span's first pixel: D_DrawSpans16 never reloads s from snext, it keeps stepping
 	 * (s += sstep eight times, sstep = (snext - s) >> 3), so every later chunk start is congruent to
@@ -789,8 +885,8 @@ RC_HD void rc_chunk_setup( const rc_view_t *vw, const rc_surf_t *sf, int32_t sky
 		int32_t snext = rc_clamp_st( rc_f2i( sdivz * z ) + sf->sadjust, sf->bbextents, px );
 		int32_t tnext = rc_clamp_st( rc_f2i( tdivz * z ) + sf->tadjust, sf->bbextentt, px );
 		int sh = kind == RC_KIND_TURB ? 4 : 3;
-		c->sstep = ( snext - s ) >> sh;
-		c->tstep = ( tnext - t ) >> sh;
+		sstep = ( snext - s ) >> sh;
+		tstep = ( tnext - t ) >> sh;
 	}
 	else if( spancount > 1 )
 	{
@@ -801,15 +897,42 @@ RC_HD void rc_chunk_setup( const rc_view_t *vw, const rc_surf_t *sf, int32_t sky
 		z = (float)0x10000 / zi;
 		int32_t snext = rc_clamp_st( rc_f2i( sdivz * z ) + sf->sadjust, sf->bbextents, px );
 		int32_t tnext = rc_clamp_st( rc_f2i( tdivz * z ) + sf->tadjust, sf->bbextentt, px );
-		c->sstep = ( snext - s ) / ( spancount - 1 );
-		c->tstep = ( tnext - t ) / ( spancount - 1 );
+		sstep = ( snext - s ) / ( spancount - 1 );
+		tstep = ( tnext - t ) / ( spancount - 1 );
 	}
 	if( kind == RC_KIND_TURB )
 	{
 		s &= ( RC_CYCLE << 16 ) - 1;
 		t &= ( RC_CYCLE << 16 ) - 1;
 	}
-	c->s = s; c->t = t;
+	*ps = s; *pt = t; *psstep = sstep; *ptstep = tstep;
+}
+
+/*
+ * State of D_DrawSpans16 / Turbulent8 at the start of chunk j of a span (u, v, count).  The reference
+ * walks the chunks sequentially accumulating sdivz/tdivz/zi in float; chunk j repeats those j additions
+ * so that chunks can be set up independently (one lane each) with bit-identical results.
+ */
+RC_HD void rc_chunk_setup( const rc_view_t *vw, const rc_surf_t *sf, int32_t sky_color, int32_t u, int32_t v, int32_t count, int32_t j, rc_chunk_t *c )
+{
+	int32_t kind = rc_span_kind( sf );
+	int32_t px = kind == RC_KIND_TURB ? 16 : 8;
+	int32_t izi0, izistep;
+	(void)vw;
+	rc_span_z0( sf, u, v, &izi0, &izistep );
+	c->izistep = izistep;
+	c->izi = (int32_t)((uint32_t)izi0 + (uint32_t)( j * px ) * (uint32_t)izistep );
+	c->u0 = u + j * px;
+	c->kind = kind;
+	c->base = sf->cache_ofs;
+	c->width = sf->cachewidth;
+	c->s = c->t = c->sstep = c->tstep = 0;
+	if( kind == RC_KIND_SKY )
+	{
+		c->base = sky_color;
+		return;
+	}
+	rc_chunk_st( sf, kind, u, v, count, j, &c->s, &c->t, &c->sstep, &c->tstep );
 }
 
 /* texel index of pixel i (0-based inside the chunk) - "span texel indices must be integer-exact" */

@@ -5,11 +5,9 @@
  * Stage map (reference function -> kernel), all per batch:
  *   S0 k_viswalk      Mod_PointInLeaf/Mod_FatPVS/R_MarkLeaves + R_RecursiveWorldNode   one warp per view
  *   S1 k_faces        R_RenderFace/R_ClipEdge/R_EmitEdge + D_CalcGradients             one thread per (view, face)
- *      k_line_scan    active-edge count per scanline (difference array -> prefix sums)  one warp per view
- *      k_bin_edges    R_InsertNewEdges/R_StepActiveU in closed form: edge -> events     one thread per edge
  *   S2 k_cache_list   D_CacheSurface staleness test -> work list                        one thread per (face, mip)
  *      k_cache_build  R_BuildLightMap + R_DrawSurface                                   persistent CTAs, one block per (face, mip)
- *   S3 k_scanlines    R_ScanEdges/R_GenerateSpans + D_DrawSpans16/D_DrawZSpans/Turbulent8  one warp per (view, scanline)
+ *   S3 k_scanlines    R_ScanEdges/R_GenerateSpans + D_DrawSpans16/D_DrawZSpans/Turbulent8  (rc_k_scan.cuh) block per 64 scanlines
  *
  * The per-item arithmetic is rc_core.h (shared with the CPU debug harness); this file is the parallel
  * decomposition, the memory layout and the stream plumbing.  Compiled with -fmad=false and IEEE
@@ -40,7 +38,7 @@ struct rc_work_t
 {
 	const rc_view_t *views;
 	int32_t nviews, width, height, clear;
-	int32_t max_cands, max_edges, max_events; /* per-view capacities */
+	int32_t max_cands, max_edges; /* per-view capacities */
 	int32_t visbytes_padded, nodewords, leafwords, surfwords, stack_ints;
 	uint8_t   *leafvis;
 	uint32_t  *nodevis, *leafmark, *surfmark;
@@ -49,24 +47,19 @@ struct rc_work_t
 	rc_surf_t *surfs;
 	rc_edge_t *edges;
 	int32_t   *ncands, *nedges;
-	int32_t   *linecnt;   /* [nviews][height + 1] difference array, then active-edge count per scanline */
-	int32_t   *lineofs;   /* [nviews][height] first event of the scanline in the view's event arena */
-	int32_t   *linecur;   /* [nviews][height] fill cursor */
-	rc_event_t *events;   /* [nviews][max_events] */
 	uint32_t  *cache_need;/* [numsurfaces * 4 bits] */
 	rc_cachekey_t *cache_keys; /* [numsurfaces * 4] */
 	int32_t   *cache_list;/* [numsurfaces * 4] work list of surf * 4 + mip */
 	int32_t   *cache_nlist, *cache_cursor;
 	const int32_t *styles;/* [256] g_lightstylevalue */
+	uint32_t  *scanbits;  /* surface bit sets of the scanline kernel when a view lists > 2015 faces, else NULL */
+	int32_t    scanbits_words, pad1;
 	uint16_t  *color;
 	int16_t   *zbuf;
 	unsigned long long *counters;
 };
 
-#define SCAN_WARPS   4
-#define SCAN_EVCAP   512 /* active edges per scanline the shared-memory sorter takes */
-#define SCAN_STKCAP  128 /* surface stack depth per scanline */
-#define SCAN_NEGCAP  16
+#define SCAN_NEGCAP  16 /* surfaces with an inverted span (trailing edge first) tracked per scanline */
 #define CACHE_THREADS 256
 #define CACHE_LUXCAP 2048
 
@@ -124,8 +117,6 @@ __global__ void __launch_bounds__( 32 ) k_viswalk( rc_scene_t sc, rc_work_t w )
 		atomicAdd( &w.counters[RC_CTR_PIXELS], (unsigned long long)vw->vrect[2] * vw->vrect[3] );
 		if( overflow ) atomicAdd( &w.counters[RC_CTR_OVERFLOW_STACK], 1ull );
 	}
-	for( int i = lane; i <= w.height; i += 32 )
-		w.linecnt[(size_t)view * ( w.height + 1 ) + i] = 0;
 }
 
 /* ---------------------------------------------------------------------------------------------- */
@@ -164,18 +155,6 @@ __global__ void __launch_bounds__( 128 ) k_faces( rc_scene_t sc, rc_work_t w )
 	*out = o;
 
 	int32_t nout = fs.nout < fs.maxout ? fs.nout : fs.maxout;
-	int32_t *lc = w.linecnt + (size_t)view * ( w.height + 1 );
-	for( int32_t k = 0; k < nout; k++ )
-	{
-		uint32_t vv = fs.out[k].vv;
-		int32_t v = (int32_t)( vv & 0xFFFF ), v2 = (int32_t)( vv >> 16 );
-		if( v2 >= w.height ) v2 = w.height - 1;
-		if( v <= v2 )
-		{
-			atomicAdd( &lc[v], 1 );
-			atomicAdd( &lc[v2 + 1], -1 );
-		}
-	}
 	/* unused reservations become edges that are never active */
 	for( int32_t k = nout; k < fs.maxout; k++ )
 	{
@@ -192,74 +171,6 @@ __global__ void __launch_bounds__( 128 ) k_faces( rc_scene_t sc, rc_work_t w )
 		}
 	}
 	atomicAdd( &w.counters[RC_CTR_EDGES], (unsigned long long)nout );
-}
-
-/* difference array -> active edges per scanline -> exclusive offsets into the view's event arena */
-__global__ void __launch_bounds__( 32 ) k_line_scan( rc_work_t w )
-{
-	const int view = blockIdx.x, lane = threadIdx.x;
-	int32_t *lc = w.linecnt + (size_t)view * ( w.height + 1 );
-	int32_t *lo = w.lineofs + (size_t)view * w.height;
-	int32_t *cur = w.linecur + (size_t)view * w.height;
-	int32_t active = 0, ofs = 0;
-	for( int base = 0; base < w.height; base += 32 )
-	{
-		int y = base + lane;
-		int32_t d = y < w.height ? lc[y] : 0;
-		/* inclusive scan of the deltas */
-		int32_t x = d;
-		for( int s = 1; s < 32; s <<= 1 )
-		{
-			int32_t t = __shfl_up_sync( 0xFFFFFFFFu, x, s );
-			if( lane >= s ) x += t;
-		}
-		int32_t cnt = active + x;
-		active += __shfl_sync( 0xFFFFFFFFu, x, 31 );
-		/* exclusive scan of the counts */
-		int32_t e = cnt;
-		for( int s = 1; s < 32; s <<= 1 )
-		{
-			int32_t t = __shfl_up_sync( 0xFFFFFFFFu, e, s );
-			if( lane >= s ) e += t;
-		}
-		if( y < w.height )
-		{
-			lc[y] = cnt;
-			lo[y] = ofs + e - cnt;
-			cur[y] = 0;
-		}
-		ofs += __shfl_sync( 0xFFFFFFFFu, e, 31 );
-	}
-	if( lane == 0 && ofs > w.max_events )
-		atomicAdd( &w.counters[RC_CTR_OVERFLOW_EVENTS], 1ull );
-}
-
-/* every edge drops one event {u at y, surfaces} into each scanline it crosses */
-__global__ void __launch_bounds__( 128 ) k_bin_edges( rc_work_t w )
-{
-	const int view = blockIdx.y;
-	const int ei = blockIdx.x * blockDim.x + threadIdx.x;
-	int32_t ne = w.nedges[view];
-	if( ne > w.max_edges ) ne = w.max_edges;
-	if( ei >= ne )
-		return;
-	const rc_edge_t e = w.edges[(size_t)view * w.max_edges + ei];
-	int32_t v = (int32_t)( e.vv & 0xFFFF ), v2 = (int32_t)( e.vv >> 16 );
-	if( v2 >= w.height ) v2 = w.height - 1;
-	const int32_t *lo = w.lineofs + (size_t)view * w.height;
-	int32_t *cur = w.linecur + (size_t)view * w.height;
-	rc_event_t *ev = w.events + (size_t)view * w.max_events;
-	uint32_t u = (uint32_t)e.u;
-	for( int32_t y = v; y <= v2; y++ )
-	{
-		int32_t slot = lo[y] + atomicAdd( &cur[y], 1 );
-		if( slot < w.max_events )
-		{
-			ev[slot].u = (int32_t)u;
-			ev[slot].surfs = e.surfs;
-		}
-		u += (uint32_t)e.u_step;
-	}
 }
 
 /* ---------------------------------------------------------------------------------------------- */
@@ -339,163 +250,7 @@ __global__ void __launch_bounds__( CACHE_THREADS ) k_cache_build( rc_scene_t sc,
 	}
 }
 
-/* ---------------------------------------------------------------------------------------------- */
-/* S3: scanlines - sort the active edges, replay them against the surface stack, draw the spans      */
-
-struct rc_scan_smem_t
-{
-	unsigned long long keys[SCAN_EVCAP];   /* sort keys, then rc_event_t in place */
-	rc_span_t spans[SCAN_EVCAP + 2];
-	int32_t   chunk0[SCAN_EVCAP + 2];      /* first chunk of each span */
-	int32_t   stk[SCAN_STKCAP], cnt[SCAN_STKCAP], neg[2 * SCAN_NEGCAP];
-	int32_t   nspans, overflow;
-};
-
-__global__ void __launch_bounds__( SCAN_WARPS * 32 ) k_scanlines( rc_scene_t sc, rc_work_t w )
-{
-	extern __shared__ __align__( 16 ) unsigned char smem_raw[];
-	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-	rc_scan_smem_t *S = reinterpret_cast<rc_scan_smem_t *>( smem_raw ) + warp;
-
-	const int view = blockIdx.y;
-	const int y = blockIdx.x * SCAN_WARPS + warp;
-	const rc_view_t *vw = &w.views[view];
-	const int x0 = vw->vrect[0], y0 = vw->vrect[1], vw_w = vw->vrect[2], vw_h = vw->vrect[3];
-	if( y < y0 || y >= y0 + vw_h || y >= w.height )
-		return;
-
-	/* 1. this scanline's events */
-	int32_t n = w.linecnt[(size_t)view * ( w.height + 1 ) + y];
-	const int32_t ofs = w.lineofs[(size_t)view * w.height + y];
-	if( ofs + n > w.max_events ) n = w.max_events - ofs > 0 ? w.max_events - ofs : 0;
-	bool overflow = false;
-	if( n > SCAN_EVCAP ) { n = SCAN_EVCAP; overflow = true; }
-	const rc_event_t *gev = w.events + (size_t)view * w.max_events + ofs;
-	int32_t npow = 32;
-	while( npow < n ) npow <<= 1;
-	for( int i = lane; i < npow; i += 32 )
-	{
-		unsigned long long k = ~0ull;
-		if( i < n )
-		{
-			rc_event_t e = gev[i];
-			k = rc_event_key( e.u, e.surfs );
-		}
-		S->keys[i] = k;
-	}
-	__syncwarp();
-
-	/* 2. bitonic sort */
-	for( int k = 2; k <= npow; k <<= 1 )
-		for( int j = k >> 1; j > 0; j >>= 1 )
-		{
-			for( int i = lane; i < npow; i += 32 )
-			{
-				int ixj = i ^ j;
-				if( ixj > i )
-				{
-					unsigned long long a = S->keys[i], b = S->keys[ixj];
-					bool up = ( i & k ) == 0;
-					if(( a > b ) == up ) { S->keys[i] = b; S->keys[ixj] = a; }
-				}
-			}
-			__syncwarp();
-		}
-	rc_event_t *ev = reinterpret_cast<rc_event_t *>( S->keys );
-	for( int i = lane; i < n; i += 32 )
-	{
-		unsigned long long k = S->keys[i];
-		rc_event_t e;
-		e.u = (int32_t)((uint32_t)( k >> 32 ) ^ 0x80000000u );
-		e.surfs = (uint32_t)k;
-		ev[i] = e;
-	}
-	__syncwarp();
-
-	/* 3. span generation (serial replay of the sorted edges) */
-	if( lane == 0 )
-	{
-		int32_t ovf = overflow ? 1 : 0;
-		const int32_t head_iu = x0, tail_u = (( x0 + vw_w ) << 20 ) + 0xFFFFF;
-		S->nspans = rc_generate_spans( ev, n, head_iu, tail_u, S->stk, S->cnt, SCAN_STKCAP, S->neg, SCAN_NEGCAP,
-			S->spans, SCAN_EVCAP + 2, &ovf );
-		S->overflow = ovf;
-	}
-	__syncwarp();
-	const int32_t nspans = S->nspans;
-
-	/* 4. chunk table: span i owns chunks [chunk0[i], chunk0[i+1]) */
-	const rc_surf_t *vsurfs = w.surfs + (size_t)view * w.max_cands;
-	int32_t total = 0;
-	for( int base = 0; base < nspans; base += 32 )
-	{
-		int i = base + lane;
-		int32_t c = 0;
-		if( i < nspans )
-		{
-			const rc_span_t sp = S->spans[i];
-			if( sp.surf )
-				c = rc_span_nchunks( rc_span_kind( &vsurfs[sp.surf - 1] ), sp.count );
-			else if( w.clear )
-				c = ( sp.count + 7 ) >> 3;
-		}
-		int32_t x = c;
-		for( int s = 1; s < 32; s <<= 1 )
-		{
-			int32_t t = __shfl_up_sync( 0xFFFFFFFFu, x, s );
-			if( lane >= s ) x += t;
-		}
-		if( i < nspans ) S->chunk0[i] = total + x - c;
-		total += __shfl_sync( 0xFFFFFFFFu, x, 31 );
-	}
-	if( lane == 0 ) S->chunk0[nspans] = total;
-	__syncwarp();
-
-	/* 5. draw: one lane per chunk of 8 (16 for turbulent) pixels */
-	const int32_t *turb = sc.sintable + vw->turb_phase;
-	uint16_t *crow = w.color + ((size_t)view * w.height + y ) * w.width;
-	int16_t *zrow = w.zbuf + ((size_t)view * w.height + y ) * w.width;
-	for( int32_t c = lane; c < total; c += 32 )
-	{
-		int lo = 0, hi = nspans - 1;
-		while( lo < hi )
-		{
-			int mid = ( lo + hi + 1 ) >> 1;
-			if( S->chunk0[mid] <= c ) lo = mid; else hi = mid - 1;
-		}
-		const rc_span_t sp = S->spans[lo];
-		const int32_t j = c - S->chunk0[lo];
-		if( !sp.surf )
-		{
-			int32_t u = sp.u + j * 8, cnt = min( 8, sp.count - j * 8 );
-			for( int i = 0; i < cnt; i++ ) { crow[u + i] = 0; zrow[u + i] = 0; }
-			continue;
-		}
-		const rc_surf_t *sf = &vsurfs[sp.surf - 1];
-		rc_chunk_t ch;
-		rc_chunk_setup( vw, sf, vw->sky_color, sp.u, y, sp.count, j, &ch );
-		const int32_t cpx = ch.kind == RC_KIND_TURB ? 16 : 8;
-		const int32_t cnt = min( cpx, sp.count - j * cpx );
-		if( ch.kind == RC_KIND_SKY )
-		{
-			for( int i = 0; i < cnt; i++ ) { crow[ch.u0 + i] = (uint16_t)ch.base; zrow[ch.u0 + i] = rc_pixel_z( &ch, i ); }
-		}
-		else
-		{
-			const uint16_t *src = ch.kind == RC_KIND_TURB ? sc.texels : sc.cache;
-			for( int i = 0; i < cnt; i++ )
-			{
-				crow[ch.u0 + i] = src[rc_pixel_texel( &ch, i, turb )];
-				zrow[ch.u0 + i] = rc_pixel_z( &ch, i );
-			}
-		}
-	}
-	if( lane == 0 )
-	{
-		atomicAdd( &w.counters[RC_CTR_SPANS], (unsigned long long)nspans );
-		if( S->overflow ) atomicAdd( &w.counters[RC_CTR_OVERFLOW_EVENTS], 1ull );
-	}
-}
+#include "rc_k_scan.cuh"
 
 /* ---------------------------------------------------------------------------------------------- */
 /* host side of the C layer                                                                          */
@@ -585,7 +340,6 @@ int ensure_batch( int nviews, int width, int height )
 	w.max_cands = sc.numsurfaces < 65000 ? ( sc.numsurfaces > 0 ? sc.numsurfaces : 1 ) : 65000;
 	long long me = (long long)sc.numsurfedges + sc.numsurfaces + 64;
 	w.max_edges = (int32_t)( me < 262144 ? me : 262144 );
-	w.max_events = height * 192;
 	w.visbytes_padded = ( sc.visbytes + 15 ) & ~15;
 	w.nodewords = ( sc.numnodes + 31 ) / 32 + 1;
 	w.leafwords = ( sc.numleafs + 31 ) / 32 + 1;
@@ -604,10 +358,9 @@ int ensure_batch( int nviews, int width, int height )
 	WALLOC( edges, rc_edge_t, (size_t)cap * w.max_edges );
 	WALLOC( ncands, int32_t, cap );
 	WALLOC( nedges, int32_t, cap );
-	WALLOC( linecnt, int32_t, (size_t)cap * ( height + 1 ));
-	WALLOC( lineofs, int32_t, (size_t)cap * height );
-	WALLOC( linecur, int32_t, (size_t)cap * height );
-	WALLOC( events, rc_event_t, (size_t)cap * w.max_events );
+	w.scanbits = nullptr; w.scanbits_words = ( w.max_cands + 32 ) / 32;
+	if( w.scanbits_words > SC_BITWORDS )
+		WALLOC( scanbits, uint32_t, (size_t)cap * (( height + SC_LINES - 1 ) / SC_LINES ) * SC_LINES * w.scanbits_words );
 	WALLOC( color, uint16_t, (size_t)cap * width * height );
 	WALLOC( zbuf, int16_t, (size_t)cap * width * height );
 #undef WALLOC
@@ -638,9 +391,6 @@ int run_stages( bool timed )
 	{
 		dim3 g(( w.max_cands + 127 ) / 128, w.nviews );
 		k_faces<<<g, 128, 0, st>>>( sc, w ); D.launches++;
-		k_line_scan<<<w.nviews, 32, 0, st>>>( w ); D.launches++;
-		dim3 g2(( w.max_edges + 127 ) / 128, w.nviews );
-		k_bin_edges<<<g2, 128, 0, st>>>( w ); D.launches++;
 	}
 	if( timed ) CK( cudaEventRecord( D.ev[2], st ));
 	{
@@ -650,8 +400,9 @@ int run_stages( bool timed )
 	}
 	if( timed ) CK( cudaEventRecord( D.ev[3], st ));
 	{
-		dim3 g(( w.height + SCAN_WARPS - 1 ) / SCAN_WARPS, w.nviews );
-		k_scanlines<<<g, SCAN_WARPS * 32, sizeof( rc_scan_smem_t ) * SCAN_WARPS, st>>>( sc, w ); D.launches++;
+		const rc_scan_layout_t lay = rc_scan_layout( w.width );
+		dim3 g(( w.height + SC_LINES - 1 ) / SC_LINES, w.nviews );
+		k_scanlines<<<g, SC_THREADS, lay.bytes, st>>>( sc, w, lay.chunkcap, lay.unionbytes ); D.launches++;
 	}
 	if( timed ) CK( cudaEventRecord( D.ev[4], st ));
 	CK( cudaGetLastError());
@@ -678,7 +429,7 @@ int rc_dev_init( int device )
 	D.device = device;
 	CK( cudaStreamCreateWithFlags( &D.stream, cudaStreamNonBlocking ));
 	for( auto &e : D.ev ) CK( cudaEventCreate( &e ));
-	CK( cudaFuncSetAttribute( k_scanlines, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)( sizeof( rc_scan_smem_t ) * SCAN_WARPS )));
+	CK( cudaFuncSetAttribute( k_scanlines, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_scan_layout( 1920 ).bytes ));
 	for( int i = 0; i < 256; i++ ) D.h_styles[i] = 256;
 	if( upload( &D.d_styles, D.h_styles, 256 ) != 0 ) return -1;
 	if( dalloc( &D.d_counters, RC_CTR_COUNT ) != 0 ) return -1;
