@@ -202,7 +202,9 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 				std::vector<uint32_t> bits(( ncands + 32 ) / 32 + 1, 0u );
 				std::vector<rc_span_t> spans2( spans.size());
 				int32_t exc[32], ovf2 = 0;
-				int ns2 = rc_generate_spans_bits( ev.data(), (int)ev.size(), head_iu, tail_u, bits.data(), (int)bits.size(), exc, 16,
+				std::vector<unsigned long long> keys( ev.size());
+				for( size_t k = 0; k < ev.size(); k++ ) keys[k] = rc_event_key( ev[k].u, ev[k].surfs );
+				int ns2 = rc_generate_spans_bits( keys.data(), (int)ev.size(), head_iu, tail_u, bits.data(), (int)bits.size(), exc, 16,
 					spans2.data(), (int)spans2.size(), &ovf2 );
 				bool same = ns2 == ns && ovf2 == ovf;
 				for( int k = 0; same && k < ns; k++ )

@@ -697,21 +697,29 @@ RC_HD int32_t rc_generate_spans( const rc_event_t *ev, int32_t nev, int32_t head
  * (world keys are unique and equal the candidate order, so "smallest key" = lowest set bit).  A surface's
  * spanstate is 0 or 1 except on degenerate scanlines (inverted spans, a surface entered twice); those few
  * live in the exception list exc[] = {surf, spanstate} with spanstate outside {0, 1}.
- * bits: (maxsurf + 32) / 32 words, zeroed by the caller.  Returns the number of spans written.
+ * keys: the line's events as sorted rc_event_key values.  bits: (maxsurf + 32) / 32 words, zeroed by the caller.
+ * Returns the number of spans written.
  */
-RC_HD int32_t rc_generate_spans_bits( const rc_event_t *ev, int32_t nev, int32_t head_iu, int32_t tail_u,
+RC_HD int32_t rc_generate_spans_bits( const unsigned long long *keys, int32_t nev, int32_t head_iu, int32_t tail_u,
 	uint32_t *bits, int32_t nwords, int32_t *exc, int32_t exccap, rc_span_t *spans, int32_t maxspans, int32_t *overflow )
 {
 	int32_t nexc = 0, nspans = 0;
 	int32_t top = 0, top_last_u = head_iu; /* 0 = background (surfaces[1], key 0x7FFFFFFF) */
+	unsigned long long k0 = nev > 0 ? keys[0] : 0ull, k1 = nev > 1 ? keys[1] : 0ull, k2 = nev > 2 ? keys[2] : 0ull, k3 = nev > 3 ? keys[3] : 0ull;
 
 #define RC_EMIT_SPAN( SURF, LAST, IU ) \
 	if(( IU ) > ( LAST )) { if( nspans < maxspans ) { spans[nspans].u = (int16_t)( LAST ); spans[nspans].count = (int16_t)(( IU ) - ( LAST )); spans[nspans].surf = ( SURF ); nspans++; } else *overflow = 1; }
 
 	for( int32_t e = 0; e < nev; e++ )
 	{
-		const int32_t u = ev[e].u;
-		const uint32_t both = ev[e].surfs;
+		/* keys are rc_event_key values: (u ^ sign bit) << 32 | surfaces; spans may overwrite the key array
+		 * (span k is written after key k was read) */
+		/* four keys in flight while earlier events are replayed (spans written so far sit at slots <= e) */
+		const unsigned long long key = k0;
+		k0 = k1; k1 = k2; k2 = k3;
+		if( e + 4 < nev ) k3 = keys[e + 4];
+		const int32_t u = (int32_t)((uint32_t)( key >> 32 ) ^ 0x80000000u );
+		const uint32_t both = (uint32_t)key;
 		if( u > tail_u )
 			break;
 		const int32_t iu = u >> 20;

@@ -7,7 +7,8 @@
  *   S1 k_faces        R_RenderFace/R_ClipEdge/R_EmitEdge + D_CalcGradients             one thread per (view, face)
  *   S2 k_cache_list   D_CacheSurface staleness test -> work list                        one thread per (face, mip)
  *      k_cache_build  R_BuildLightMap + R_DrawSurface                                   persistent CTAs, one block per (face, mip)
- *   S3 k_scanlines    R_ScanEdges/R_GenerateSpans + D_DrawSpans16/D_DrawZSpans/Turbulent8  (rc_k_scan.cuh) block per 64 scanlines
+ *   S3 k_spans        R_ScanEdges/R_GenerateSpans (rc_k_spans.cuh)                      one thread per (view, scanline)
+ *      k_draw         D_DrawSpans16/D_DrawZSpans/Turbulent8/D_BackgroundSurf (rc_k_draw.cuh) one warp per (view, scanline)
  *
  * The per-item arithmetic is rc_core.h (shared with the CPU debug harness); this file is the parallel
  * decomposition, the memory layout and the stream plumbing.  Compiled with -fmad=false and IEEE
@@ -34,6 +35,8 @@ struct rc_cachekey_t
 	int32_t pad[2];
 }; /* 32 B: what D_CacheSurface compares (r_surf.c:1090-1120): texture, light style values */
 
+struct rc_lineinfo_t { int32_t ofs, nsp; }; /* span slice of a scanline: first slot inside the view's arena, count */
+
 struct rc_work_t
 {
 	const rc_view_t *views;
@@ -52,14 +55,20 @@ struct rc_work_t
 	int32_t   *cache_list;/* [numsurfaces * 4] work list of surf * 4 + mip */
 	int32_t   *cache_nlist, *cache_cursor;
 	const int32_t *styles;/* [256] g_lightstylevalue */
-	uint32_t  *scanbits;  /* surface bit sets of the scanline kernel when a view lists > 2015 faces, else NULL */
-	int32_t    scanbits_words, pad1;
+	uint32_t  *scanbits;  /* surface bit sets of k_spans when a view lists > 2015 faces, else NULL */
+	int32_t    scanbits_words, nbands;
+	int32_t   *bandcnt;   /* [nviews][nbands] edges binned per band of SP_LINES scanlines */
+	rc_edge_t *bandedges; /* [nviews][nbands][band_cap] */
+	int32_t    band_cap, blk_events; /* capacities: edges per band, event/span slots per band */
+	size_t     view_events;          /* nbands * blk_events */
+	unsigned long long *events;      /* [nviews][nbands][blk_events] sort keys, then rc_span_t in place */
+	rc_lineinfo_t *lineinfo;         /* [nviews][height] span slice of every scanline */
 	uint16_t  *color;
 	int16_t   *zbuf;
 	unsigned long long *counters;
 };
 
-#define SCAN_NEGCAP  16 /* surfaces with an inverted span (trailing edge first) tracked per scanline */
+#define SP_LINES 64 /* scanlines per band (rc_k_spans.cuh): k_faces bins edges by band */
 #define CACHE_THREADS 256
 #define CACHE_LUXCAP 2048
 
@@ -155,6 +164,21 @@ __global__ void __launch_bounds__( 128 ) k_faces( rc_scene_t sc, rc_work_t w )
 	*out = o;
 
 	int32_t nout = fs.nout < fs.maxout ? fs.nout : fs.maxout;
+	/* every edge also goes to the list of each band of SP_LINES scanlines it crosses (k_spans reads those) */
+	for( int32_t k = 0; k < nout; k++ )
+	{
+		const rc_edge_t e = fs.out[k];
+		int32_t v = (int32_t)( e.vv & 0xFFFF ), v2 = (int32_t)( e.vv >> 16 );
+		if( v2 >= w.height ) v2 = w.height - 1;
+		for( int32_t b = v / SP_LINES; b <= v2 / SP_LINES; b++ )
+		{
+			const int32_t slot = atomicAdd( &w.bandcnt[view * w.nbands + b], 1 );
+			if( slot < w.band_cap )
+				w.bandedges[((size_t)view * w.nbands + b ) * w.band_cap + slot] = e;
+			else if( slot == w.band_cap )
+				atomicAdd( &w.counters[RC_CTR_OVERFLOW_EDGES], 1ull );
+		}
+	}
 	/* unused reservations become edges that are never active */
 	for( int32_t k = nout; k < fs.maxout; k++ )
 	{
@@ -250,7 +274,18 @@ __global__ void __launch_bounds__( CACHE_THREADS ) k_cache_build( rc_scene_t sc,
 	}
 }
 
-#include "rc_k_scan.cuh"
+__device__ __forceinline__ int32_t rc_warp_incl_scan( int32_t x, int lane )
+{
+	for( int s = 1; s < 32; s <<= 1 )
+	{
+		int32_t t = __shfl_up_sync( 0xFFFFFFFFu, x, s );
+		if( lane >= s ) x += t;
+	}
+	return x;
+}
+
+#include "rc_k_spans.cuh"
+#include "rc_k_draw.cuh"
 
 /* ---------------------------------------------------------------------------------------------- */
 /* host side of the C layer                                                                          */
@@ -358,9 +393,17 @@ int ensure_batch( int nviews, int width, int height )
 	WALLOC( edges, rc_edge_t, (size_t)cap * w.max_edges );
 	WALLOC( ncands, int32_t, cap );
 	WALLOC( nedges, int32_t, cap );
+	w.nbands = ( height + SP_LINES - 1 ) / SP_LINES;
+	w.band_cap = w.max_edges / 2 < 1024 ? 1024 : ( w.max_edges / 2 > 32768 ? 32768 : w.max_edges / 2 );
+	w.blk_events = SP_LINES * ( width / 2 > 512 ? width / 2 : 512 );
+	w.view_events = (size_t)w.nbands * w.blk_events;
 	w.scanbits = nullptr; w.scanbits_words = ( w.max_cands + 32 ) / 32;
-	if( w.scanbits_words > SC_BITWORDS )
-		WALLOC( scanbits, uint32_t, (size_t)cap * (( height + SC_LINES - 1 ) / SC_LINES ) * SC_LINES * w.scanbits_words );
+	if( w.scanbits_words > SP_BITWORDS )
+		WALLOC( scanbits, uint32_t, (size_t)cap * w.nbands * SP_LINES * w.scanbits_words );
+	WALLOC( bandcnt, int32_t, (size_t)cap * w.nbands );
+	WALLOC( bandedges, rc_edge_t, (size_t)cap * w.nbands * w.band_cap );
+	WALLOC( events, unsigned long long, (size_t)cap * w.view_events );
+	WALLOC( lineinfo, rc_lineinfo_t, (size_t)cap * height );
 	WALLOC( color, uint16_t, (size_t)cap * width * height );
 	WALLOC( zbuf, int16_t, (size_t)cap * width * height );
 #undef WALLOC
@@ -385,6 +428,7 @@ int run_stages( bool timed )
 	CK( cudaMemsetAsync( D.d_counters, 0, sizeof( unsigned long long ) * RC_CTR_COUNT, st ));
 	CK( cudaMemsetAsync( D.d_need, 0, sizeof( uint32_t ) * (( sc.numsurfaces * 4 + 31 ) / 32 + 1 ), st ));
 	CK( cudaMemsetAsync( D.d_nlist, 0, sizeof( int32_t ) * 2, st ));
+	CK( cudaMemsetAsync( w.bandcnt, 0, sizeof( int32_t ) * (size_t)w.nviews * w.nbands, st ));
 	if( timed ) CK( cudaEventRecord( D.ev[0], st ));
 	k_viswalk<<<w.nviews, 32, 0, st>>>( sc, w ); D.launches++;
 	if( timed ) CK( cudaEventRecord( D.ev[1], st ));
@@ -400,9 +444,11 @@ int run_stages( bool timed )
 	}
 	if( timed ) CK( cudaEventRecord( D.ev[3], st ));
 	{
-		const rc_scan_layout_t lay = rc_scan_layout( w.width );
-		dim3 g(( w.height + SC_LINES - 1 ) / SC_LINES, w.nviews );
-		k_scanlines<<<g, SC_THREADS, lay.bytes, st>>>( sc, w, lay.chunkcap, lay.unionbytes ); D.launches++;
+		dim3 g( w.nbands, w.nviews );
+		k_spans<<<g, SP_THREADS, 0, st>>>( w ); D.launches++;
+		const int32_t chunkcap = ( w.width + 7 ) / 8 + SC_SPCAP + 1;
+		dim3 g2(( w.height + DR_WARPS - 1 ) / DR_WARPS, w.nviews );
+		k_draw<<<g2, DR_WARPS * 32, rc_draw_smem( chunkcap ), st>>>( sc, w, chunkcap ); D.launches++;
 	}
 	if( timed ) CK( cudaEventRecord( D.ev[4], st ));
 	CK( cudaGetLastError());
@@ -429,7 +475,7 @@ int rc_dev_init( int device )
 	D.device = device;
 	CK( cudaStreamCreateWithFlags( &D.stream, cudaStreamNonBlocking ));
 	for( auto &e : D.ev ) CK( cudaEventCreate( &e ));
-	CK( cudaFuncSetAttribute( k_scanlines, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_scan_layout( 1920 ).bytes ));
+	CK( cudaFuncSetAttribute( k_draw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_draw_smem(( 1920 + 7 ) / 8 + SC_SPCAP + 1 )));
 	for( int i = 0; i < 256; i++ ) D.h_styles[i] = 256;
 	if( upload( &D.d_styles, D.h_styles, 256 ) != 0 ) return -1;
 	if( dalloc( &D.d_counters, RC_CTR_COUNT ) != 0 ) return -1;
