@@ -43,9 +43,7 @@ struct rc_work_t
 	int32_t nviews, width, height, clear;
 	int32_t max_cands, max_edges; /* per-view capacities */
 	int32_t visbytes_padded, nodewords, leafwords, surfwords, stack_ints;
-	uint8_t   *leafvis;
-	uint32_t  *nodevis, *leafmark, *surfmark;
-	int32_t   *walkstack;
+	int32_t   *walkstack; /* [nviews][stack_ints] k_viswalk scratch (rc_vis_scratch_ints) */
 	rc_cand_t *cands;
 	rc_surf_t *surfs;
 	rc_edge_t *edges;
@@ -72,61 +70,20 @@ struct rc_work_t
 #define CACHE_THREADS 256
 #define CACHE_LUXCAP 2048
 
+__device__ __forceinline__ int32_t rc_warp_incl_scan( int32_t x, int lane )
+{
+	for( int s = 1; s < 32; s <<= 1 )
+	{
+		int32_t t = __shfl_up_sync( 0xFFFFFFFFu, x, s );
+		if( lane >= s ) x += t;
+	}
+	return x;
+}
+
 /* ---------------------------------------------------------------------------------------------- */
 /* S0: visibility + BSP walk                                                                         */
 
-__global__ void __launch_bounds__( 32 ) k_viswalk( rc_scene_t sc, rc_work_t w )
-{
-	const int view = blockIdx.x, lane = threadIdx.x;
-	const rc_view_t *vw = &w.views[view];
-	uint8_t  *vis = w.leafvis + (size_t)view * w.visbytes_padded;
-	uint32_t *nodevis = w.nodevis + (size_t)view * w.nodewords;
-	uint32_t *leafmark = w.leafmark + (size_t)view * w.leafwords;
-	uint32_t *surfmark = w.surfmark + (size_t)view * w.surfwords;
-	int32_t  *stack = w.walkstack + (size_t)view * w.stack_ints;
-
-	for( int i = lane; i < w.nodewords; i += 32 ) nodevis[i] = 0;
-	for( int i = lane; i < w.leafwords; i += 32 ) leafmark[i] = 0;
-	for( int i = lane; i < w.surfwords; i += 32 ) surfmark[i] = 0;
-
-	if( vw->pvs_radius < 0 )
-	{
-		for( int i = lane; i < w.visbytes_padded; i += 32 ) vis[i] = 0xFF;
-	}
-	else if( lane == 0 )
-		rc_fat_pvs( &sc, vw->origin, vw->pvs_radius, vis, stack, w.stack_ints );
-	__syncwarp();
-
-	/* R_MarkLeaves: lanes take clusters; a lane stops climbing where another one already passed */
-	for( int i = lane; i < sc.numclusters; i += 32 )
-	{
-		if( !( vis[i >> 3] & ( 1 << ( i & 7 ))))
-			continue;
-		atomicOr( &leafmark[( i + 1 ) >> 5], 1u << (( i + 1 ) & 31 ));
-		int32_t node = sc.leafs[i + 1].parent;
-		while( node >= 0 )
-		{
-			uint32_t bit = 1u << ( node & 31 );
-			if( atomicOr( &nodevis[node >> 5], bit ) & bit )
-				break;
-			node = sc.nodes[node].parent;
-		}
-	}
-	__syncwarp();
-
-	if( lane == 0 )
-	{
-		int32_t overflow = 0;
-		int32_t n = rc_walk_world( &sc, vw, nodevis, leafmark, surfmark, stack, w.stack_ints,
-			w.cands + (size_t)view * w.max_cands, w.max_cands, &overflow );
-		w.ncands[view] = n;
-		w.nedges[view] = 0;
-		atomicAdd( &w.counters[RC_CTR_CANDS], (unsigned long long)n );
-		atomicAdd( &w.counters[RC_CTR_VIEWS], 1ull );
-		atomicAdd( &w.counters[RC_CTR_PIXELS], (unsigned long long)vw->vrect[2] * vw->vrect[3] );
-		if( overflow ) atomicAdd( &w.counters[RC_CTR_OVERFLOW_STACK], 1ull );
-	}
-}
+#include "rc_k_vis.cuh"
 
 /* ---------------------------------------------------------------------------------------------- */
 /* S1: faces -> surf_t records + edges                                                               */
@@ -274,16 +231,6 @@ __global__ void __launch_bounds__( CACHE_THREADS ) k_cache_build( rc_scene_t sc,
 	}
 }
 
-__device__ __forceinline__ int32_t rc_warp_incl_scan( int32_t x, int lane )
-{
-	for( int s = 1; s < 32; s <<= 1 )
-	{
-		int32_t t = __shfl_up_sync( 0xFFFFFFFFu, x, s );
-		if( lane >= s ) x += t;
-	}
-	return x;
-}
-
 #include "rc_k_spans.cuh"
 #include "rc_k_draw.cuh"
 
@@ -379,14 +326,10 @@ int ensure_batch( int nviews, int width, int height )
 	w.nodewords = ( sc.numnodes + 31 ) / 32 + 1;
 	w.leafwords = ( sc.numleafs + 31 ) / 32 + 1;
 	w.surfwords = ( sc.numsurfaces + 31 ) / 32 + 1;
-	w.stack_ints = 2 * ( sc.maxdepth + 4 ) + 8;
+	w.stack_ints = (int32_t)rc_vis_scratch_ints( sc.numnodes );
 
 	int k = 0;
 #define WALLOC( field, type, count ) do { type *p = nullptr; if( dalloc( &p, (size_t)( count )) != 0 ) return -1; w.field = p; D.d_work[k++] = p; } while( 0 )
-	WALLOC( leafvis, uint8_t, (size_t)cap * w.visbytes_padded );
-	WALLOC( nodevis, uint32_t, (size_t)cap * w.nodewords );
-	WALLOC( leafmark, uint32_t, (size_t)cap * w.leafwords );
-	WALLOC( surfmark, uint32_t, (size_t)cap * w.surfwords );
 	WALLOC( walkstack, int32_t, (size_t)cap * w.stack_ints );
 	WALLOC( cands, rc_cand_t, (size_t)cap * w.max_cands );
 	WALLOC( surfs, rc_surf_t, (size_t)cap * w.max_cands );
@@ -430,7 +373,7 @@ int run_stages( bool timed )
 	CK( cudaMemsetAsync( D.d_nlist, 0, sizeof( int32_t ) * 2, st ));
 	CK( cudaMemsetAsync( w.bandcnt, 0, sizeof( int32_t ) * (size_t)w.nviews * w.nbands, st ));
 	if( timed ) CK( cudaEventRecord( D.ev[0], st ));
-	k_viswalk<<<w.nviews, 32, 0, st>>>( sc, w ); D.launches++;
+	k_viswalk<<<w.nviews, VW_THREADS, sizeof( uint32_t ) * (size_t)(( w.visbytes_padded >> 2 ) + w.nodewords + w.leafwords + w.surfwords ), st>>>( sc, w ); D.launches++;
 	if( timed ) CK( cudaEventRecord( D.ev[1], st ));
 	{
 		dim3 g(( w.max_cands + 127 ) / 128, w.nviews );
@@ -539,6 +482,40 @@ int rc_dev_upload_scene( const rc_scene_t *sc, size_t cache_texels )
 	if( upload( &visdata, sc->visdata, (size_t)sc->visdata_len ) != 0 ) return -1;
 	if( upload( &lightdata, sc->lightdata, (size_t)sc->lightdata_len ) != 0 ) return -1;
 	if( upload( &cache, (const uint16_t *)nullptr, cache_texels ) != 0 ) return -1;
+
+	/* derived tables: every leaf's PVS row expanded once (Mod_DecompressPVS, engine/common/mod_bmodel.c:1054: zero
+	 * runs are {0, count} pairs), and the node each surface hangs off */
+	uint32_t *pvsdense = (uint32_t *)D.d_scene[11]; int32_t *surfnode = (int32_t *)D.d_scene[12];
+	{
+		const int32_t vpad = ( sc->visbytes + 15 ) & ~15;
+		std::vector<uint8_t> dense((size_t)( sc->numleafs > 0 ? sc->numleafs : 1 ) * vpad, 0 );
+		for( int32_t l = 0; l < sc->numleafs; l++ )
+		{
+			uint8_t *out = dense.data() + (size_t)l * vpad;
+			const int32_t ofs = sc->leafs[l].visofs;
+			if( ofs < 0 || !sc->visdata_len )
+			{
+				memset( out, 0xFF, (size_t)sc->visbytes );
+				continue;
+			}
+			const uint8_t *in = sc->visdata + ofs, *end = sc->visdata + sc->visdata_len;
+			int32_t d = 0;
+			while( d < sc->visbytes && in < end )
+			{
+				if( *in ) out[d++] = *in++;
+				else { d += in[1]; in += 2; }
+			}
+		}
+		if( upload( &pvsdense, (const uint32_t *)dense.data(), dense.size() / 4 ) != 0 ) return -1;
+		std::vector<int32_t> sn((size_t)( sc->numsurfaces > 0 ? sc->numsurfaces : 1 ), 0 );
+		for( int32_t n = 0; n < sc->numnodes; n++ )
+			for( int32_t k = 0; k < sc->nodes[n].numsurfaces; k++ )
+				if( sc->nodes[n].firstsurface + k < sc->numsurfaces )
+					sn[sc->nodes[n].firstsurface + k] = n;
+		if( upload( &surfnode, sn.data(), sn.size()) != 0 ) return -1;
+	}
+	D.d_scene[11] = pvsdense; D.d_scene[12] = surfnode;
+	d.pvsdense = pvsdense; d.surfnode = surfnode;
 	D.d_scene[0] = planes; D.d_scene[1] = nodes; D.d_scene[2] = leafs; D.d_scene[3] = surfaces; D.d_scene[4] = marks;
 	D.d_scene[5] = surfedges; D.d_scene[6] = edges; D.d_scene[7] = verts; D.d_scene[8] = visdata; D.d_scene[9] = lightdata;
 	D.d_scene[10] = cache;

@@ -1,0 +1,344 @@
+/*
+ * rc_k_vis.cuh - S0, visibility + BSP walk of one view per block:
+ *   Mod_PointInLeaf / Mod_FatPVS (engine/common/mod_bmodel.c:1116,1203), R_MarkLeaves (ref/soft/r_main.c:1021),
+ *   R_RenderWorld / R_RecursiveWorldNode (ref/soft/r_bsp.c:466-641).
+ *
+ * The reference recurses front to back and posts faces as it goes; the only things that reach the later stages
+ * are WHICH faces are posted, with which clipflags, and in WHAT ORDER (the order is the surface key).  All three
+ * are functions of the visited part of the tree, so the walk is done level by level instead of depth first:
+ *
+ *   P1  top-down, one barrier pair per tree level: every frontier entry is tested (node visframe bit, 4-plane
+ *       bbox cull -> reduced clipflags, leaf contents/visframe); a surviving node appends its two children to the
+ *       next level, nearer child first.
+ *   P2  bottom-up: size of every visited subtree (visited node or leaf = 1).
+ *   P3  top-down: in-order position of every visited entry: [near subtree][node][far subtree] - exactly the order
+ *       the recursion reaches them in.
+ *   P4  leaf marks: surface s is marked when a visited leaf lists it AND that leaf comes before s's node in the
+ *       in-order sequence (the reference tests surf->visframe when it posts the node's faces, i.e. after the near
+ *       subtree only).
+ *   P5  faces per visited node in in-order sequence, block prefix sum, candidates written at their final index.
+ *
+ * Bit sets (PVS row, node/leaf visframe, surface marks) live in shared memory: BSP30 caps faces, leafs and nodes
+ * at 65535 each, so they never exceed 4 x 8 KB.
+ */
+#ifndef RC_K_VIS_CUH
+#define RC_K_VIS_CUH
+
+#define VW_THREADS 128
+#define VW_MAXLVL  1024
+#define VW_PVSCAP  32   /* leaves inside the fat-PVS radius handled by the parallel OR (r_pvs_radius is 0.1) */
+
+/* per-view int32 scratch: 6 arrays of cap entries + nodepos[numnodes] + leaf list[cap] */
+static inline size_t rc_vis_scratch_ints( int32_t numnodes )
+{
+	const size_t cap = 2 * (size_t)numnodes + 2;
+	return 7 * cap + (size_t)numnodes + 8;
+}
+
+__global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_work_t w )
+{
+	extern __shared__ uint32_t s_bits[];
+	__shared__ int32_t s_lvl[VW_MAXLVL + 2];
+	__shared__ int32_t s_n, s_nleaf, s_npvs, s_allvis, s_ovf;
+	__shared__ int32_t s_pvsleaf[VW_PVSCAP];
+	__shared__ int32_t s_warp[VW_THREADS / 32];
+
+	const int view = blockIdx.x, t = threadIdx.x, lane = t & 31, warp = t >> 5;
+	const rc_view_t *vw = &w.views[view];
+	const int32_t viswords = w.visbytes_padded >> 2;
+	uint32_t *vis = s_bits;
+	uint32_t *nodevis = vis + viswords;
+	uint32_t *leafmark = nodevis + w.nodewords;
+	uint32_t *surfmark = leafmark + w.leafwords;
+	const int32_t allwords = viswords + w.nodewords + w.leafwords + w.surfwords;
+
+	const int32_t cap = 2 * sc.numnodes + 2;
+	int32_t *scr = w.walkstack + (size_t)view * w.stack_ints;
+	int32_t *e_ref = scr, *e_info = scr + cap, *e_child = scr + 2 * (size_t)cap, *e_size = scr + 3 * (size_t)cap;
+	int32_t *e_pos = scr + 4 * (size_t)cap, *seq = scr + 5 * (size_t)cap, *leaflist = scr + 6 * (size_t)cap;
+	int32_t *nodepos = scr + 7 * (size_t)cap;
+
+	for( int i = t; i < allwords; i += VW_THREADS ) s_bits[i] = 0;
+	for( int i = t; i < sc.numnodes; i += VW_THREADS ) nodepos[i] = -1; /* not visited: precedes no leaf */
+	if( t == 0 )
+	{
+		s_n = 1; s_nleaf = 0; s_npvs = 0; s_allvis = 0; s_ovf = 0;
+		e_ref[0] = sc.headnode; e_info[0] = 15;
+
+		/* Mod_FatPVS: the leaves within pvs_radius of the eye (front side first, back side deferred) */
+		if( vw->pvs_radius < 0 )
+			s_allvis = 1;
+		else
+		{
+			const int32_t viewleaf = rc_point_in_leaf( &sc, vw->origin );
+			if( !sc.visdata_len || sc.leafs[viewleaf].cluster < 0 )
+				s_allvis = 1;
+			else
+			{
+				int32_t *stack = seq; /* free until P5 */
+				int32_t sp = 0, node = sc.headnode, np = 0;
+				for( ;; )
+				{
+					while( node >= 0 )
+					{
+						const rc_node_t *nd = &sc.nodes[node];
+						const float d = rc_planediff( vw->origin, &sc.planes[nd->plane] );
+						if( d > vw->pvs_radius ) node = nd->child[0];
+						else if( d < -vw->pvs_radius ) node = nd->child[1];
+						else
+						{
+							if( sp < cap ) stack[sp++] = nd->child[1];
+							node = nd->child[0];
+						}
+					}
+					const int32_t li = -1 - node;
+					if( sc.leafs[li].cluster >= 0 )
+					{
+						if( np < VW_PVSCAP ) s_pvsleaf[np++] = li;
+						else
+						{
+							/* rare: more leaves than the list holds - OR this row right here */
+							const uint32_t *row = sc.pvsdense + (size_t)li * viswords;
+							for( int32_t k = 0; k < viswords; k++ ) vis[k] |= row[k];
+						}
+					}
+					if( !sp ) break;
+					node = stack[--sp];
+				}
+				s_npvs = np;
+			}
+		}
+	}
+	__syncthreads();
+
+	/* fat PVS = OR of the (pre-expanded) rows */
+	if( s_allvis )
+	{
+		for( int i = t; i < viswords; i += VW_THREADS ) vis[i] = 0xFFFFFFFFu;
+	}
+	else
+	{
+		const int32_t np = s_npvs;
+		for( int i = t; i < viswords; i += VW_THREADS )
+		{
+			uint32_t v = vis[i];
+			for( int32_t k = 0; k < np; k++ ) v |= sc.pvsdense[(size_t)s_pvsleaf[k] * viswords + i];
+			vis[i] = v;
+		}
+	}
+	__syncthreads();
+
+	/* R_MarkLeaves: threads take clusters; a thread stops climbing where another one already passed */
+	for( int i = t; i < sc.numclusters; i += VW_THREADS )
+	{
+		if( !(( vis[i >> 5] >> ( i & 31 )) & 1 ))
+			continue;
+		atomicOr( &leafmark[( i + 1 ) >> 5], 1u << (( i + 1 ) & 31 ));
+		int32_t node = sc.leafs[i + 1].parent;
+		while( node >= 0 )
+		{
+			const uint32_t bit = 1u << ( node & 31 );
+			if( atomicOr( &nodevis[node >> 5], bit ) & bit )
+				break;
+			node = sc.nodes[node].parent;
+		}
+	}
+	__syncthreads();
+
+	/* P1: level-synchronous descent */
+	int32_t nlvl = 0;
+	if( t == 0 ) s_lvl[0] = 0;
+	for( ;; )
+	{
+		__syncthreads();
+		const int32_t a = s_lvl[nlvl], b = s_n;
+		__syncthreads();
+		if( a == b )
+			break;
+		if( nlvl + 1 > VW_MAXLVL )
+		{
+			if( t == 0 ) s_ovf = 1;
+			break;
+		}
+		if( t == 0 ) s_lvl[nlvl + 1] = b;
+		for( int32_t e = a + t; e < b; e += VW_THREADS )
+		{
+			const int32_t ref = e_ref[e];
+			int32_t clipflags = e_info[e] & 15, alive = 0, child = -1;
+			if( ref < 0 )
+			{
+				const int32_t li = -1 - ref;
+				const rc_leaf_t *leaf = &sc.leafs[li];
+				if( leaf->contents != RC_CONTENTS_SOLID && rc_testbit( leafmark, li )
+					&& !( clipflags && rc_cull_box( vw, leaf->minmaxs, clipflags ) < 0 ))
+				{
+					alive = 1;
+					leaflist[atomicAdd( &s_nleaf, 1 )] = e;
+				}
+			}
+			else if( rc_testbit( nodevis, ref ))
+			{
+				const rc_node_t *node = &sc.nodes[ref];
+				if( clipflags )
+					clipflags = rc_cull_box( vw, node->minmaxs, clipflags );
+				if( clipflags >= 0 )
+				{
+					alive = 1;
+					const int side = rc_node_dot( vw, &sc.planes[node->plane] ) >= 0 ? 0 : 1;
+					child = atomicAdd( &s_n, 2 );
+					e_ref[child] = node->child[side]; e_info[child] = clipflags;
+					e_ref[child + 1] = node->child[!side]; e_info[child + 1] = clipflags;
+				}
+				else clipflags = 0;
+			}
+			e_info[e] = clipflags | ( alive << 4 );
+			e_child[e] = child;
+		}
+		nlvl++;
+	}
+	__syncthreads();
+
+	/* P2: subtree sizes, deepest level first */
+	for( int32_t L = nlvl - 1; L >= 0; L-- )
+	{
+		const int32_t a = s_lvl[L], b = s_lvl[L + 1];
+		for( int32_t e = a + t; e < b; e += VW_THREADS )
+		{
+			int32_t sz = 0;
+			if( e_info[e] & 16 )
+			{
+				const int32_t c = e_child[e];
+				sz = 1 + ( c >= 0 ? e_size[c] + e_size[c + 1] : 0 );
+			}
+			e_size[e] = sz;
+		}
+		__syncthreads();
+	}
+
+	/* P3: in-order positions */
+	if( t == 0 ) e_pos[0] = 0;
+	__syncthreads();
+	for( int32_t L = 0; L < nlvl; L++ )
+	{
+		const int32_t a = s_lvl[L], b = s_lvl[L + 1];
+		for( int32_t e = a + t; e < b; e += VW_THREADS )
+		{
+			if( !( e_info[e] & 16 ))
+				continue;
+			const int32_t c = e_child[e], base = e_pos[e];
+			if( c >= 0 )
+			{
+				const int32_t mine = base + e_size[c];
+				e_pos[c] = base;
+				e_pos[c + 1] = mine + 1;
+				e_pos[e] = mine;
+				nodepos[e_ref[e]] = mine;
+			}
+		}
+		__syncthreads();
+	}
+
+	/* P4: leaf marks that precede the surface's node */
+	{
+		const int32_t nleaf = s_nleaf;
+		for( int32_t k = warp; k < nleaf; k += VW_THREADS / 32 )
+		{
+			const int32_t e = leaflist[k];
+			const int32_t pos = e_pos[e];
+			const rc_leaf_t *leaf = &sc.leafs[-1 - e_ref[e]];
+			const int32_t m0 = leaf->firstmark, m1 = m0 + leaf->nummark;
+			for( int32_t m = m0 + lane; m < m1; m += 32 )
+			{
+				const int32_t s = sc.marksurfaces[m];
+				if( pos < nodepos[sc.surfnode[s]] )
+					atomicOr( &surfmark[s >> 5], 1u << ( s & 31 ));
+			}
+		}
+	}
+	__syncthreads();
+
+	/* P5: faces per visited node, laid out by in-order position */
+	const int32_t nseq = nlvl ? e_size[0] : 0, nent = s_n;
+	for( int32_t e = t; e < nent; e += VW_THREADS )
+	{
+		const int32_t info = e_info[e];
+		if( !( info & 16 ))
+			continue;
+		int32_t cnt = 0;
+		const int32_t ref = e_ref[e];
+		if( ref >= 0 )
+		{
+			const rc_node_t *node = &sc.nodes[ref];
+			const int32_t c = node->numsurfaces;
+			if( c )
+			{
+				const double dot = rc_node_dot( vw, &sc.planes[node->plane] );
+				const int want = dot < -RC_BACKFACE_EPSILON ? 1 : ( dot > RC_BACKFACE_EPSILON ? 0 : -1 );
+				if( want >= 0 )
+					for( int32_t s = node->firstsurface; s < node->firstsurface + c; s++ )
+						if((( sc.surfaces[s].flags & RC_SURF_PLANEBACK ) ? 1 : 0 ) == want && rc_testbit( surfmark, s ))
+							cnt++;
+			}
+		}
+		seq[e_pos[e]] = cnt;
+	}
+	__syncthreads();
+	int32_t carry = 0;
+	for( int32_t i0 = 0; i0 < nseq; i0 += VW_THREADS )
+	{
+		const int32_t i = i0 + t;
+		const int32_t v = i < nseq ? seq[i] : 0;
+		int32_t x = rc_warp_incl_scan( v, lane );
+		if( lane == 31 ) s_warp[warp] = x;
+		__syncthreads();
+		int32_t wbase = 0, tot = 0;
+		for( int k = 0; k < VW_THREADS / 32; k++ )
+		{
+			if( k < warp ) wbase += s_warp[k];
+			tot += s_warp[k];
+		}
+		if( i < nseq ) seq[i] = carry + wbase + x - v;
+		carry += tot;
+		__syncthreads();
+	}
+	const int32_t total = carry;
+	rc_cand_t *cands = w.cands + (size_t)view * w.max_cands;
+	for( int32_t e = t; e < nent; e += VW_THREADS )
+	{
+		const int32_t info = e_info[e], ref = e_ref[e];
+		if( !( info & 16 ) || ref < 0 )
+			continue;
+		const rc_node_t *node = &sc.nodes[ref];
+		const int32_t c = node->numsurfaces;
+		if( !c )
+			continue;
+		const double dot = rc_node_dot( vw, &sc.planes[node->plane] );
+		const int want = dot < -RC_BACKFACE_EPSILON ? 1 : ( dot > RC_BACKFACE_EPSILON ? 0 : -1 );
+		if( want < 0 )
+			continue;
+		int32_t o = seq[e_pos[e]];
+		for( int32_t s = node->firstsurface; s < node->firstsurface + c; s++ )
+			if((( sc.surfaces[s].flags & RC_SURF_PLANEBACK ) ? 1 : 0 ) == want && rc_testbit( surfmark, s ))
+			{
+				if( o < w.max_cands )
+				{
+					cands[o].surf = s;
+					cands[o].clipflags = info & 15;
+				}
+				o++;
+			}
+	}
+
+	if( t == 0 )
+	{
+		w.ncands[view] = total < w.max_cands ? total : w.max_cands;
+		w.nedges[view] = 0;
+		atomicAdd( &w.counters[RC_CTR_CANDS], (unsigned long long)( total < w.max_cands ? total : w.max_cands ));
+		atomicAdd( &w.counters[RC_CTR_VIEWS], 1ull );
+		atomicAdd( &w.counters[RC_CTR_PIXELS], (unsigned long long)vw->vrect[2] * vw->vrect[3] );
+		if( s_ovf ) atomicAdd( &w.counters[RC_CTR_OVERFLOW_STACK], 1ull );
+		if( total > w.max_cands ) atomicAdd( &w.counters[RC_CTR_OVERFLOW_CANDS], 1ull );
+	}
+}
+
+#endif /* RC_K_VIS_CUH */

@@ -105,6 +105,9 @@ typedef struct
 	const uint16_t     *lightgamma;/* [1024] engine lightgammatable */
 	const int32_t      *sintable;  /* [1280] ref/soft/r_main.c:1312 */
 	uint16_t           *cache;     /* surface cache arena */
+	/* derived on upload (rc_dev_upload_scene); host callers leave them NULL */
+	const uint32_t     *pvsdense;  /* [numleafs][visbytes_padded / 4] Mod_DecompressPVS of every leaf's row */
+	const int32_t      *surfnode;  /* [numsurfaces] the node a surface hangs off */
 } rc_scene_t;
 
 /* per-view constants: everything R_SetupFrustum/R_SetupFrameQ/R_ViewChanged/R_TransformFrustum derive
