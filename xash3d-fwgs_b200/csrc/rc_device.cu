@@ -43,6 +43,7 @@ struct rc_work_t
 	int32_t nviews, width, height, clear;
 	int32_t max_cands, max_edges; /* per-view capacities */
 	int32_t visbytes_padded, nodewords, leafwords, surfwords, stack_ints;
+	int32_t vis_stage, vis_smem; /* k_viswalk: VW_STAGE_* flags and dynamic shared memory bytes */
 	int32_t   *walkstack; /* [nviews][stack_ints] k_viswalk scratch (rc_vis_scratch_ints) */
 	rc_cand_t *cands;
 	rc_surf_t *surfs;
@@ -327,6 +328,20 @@ int ensure_batch( int nviews, int width, int height )
 	w.leafwords = ( sc.numleafs + 31 ) / 32 + 1;
 	w.surfwords = ( sc.numsurfaces + 31 ) / 32 + 1;
 	w.stack_ints = (int32_t)rc_vis_scratch_ints( sc.numnodes );
+	{
+		const size_t budget = 200 * 1024;
+		size_t need = ((((size_t)( w.visbytes_padded >> 2 ) + w.nodewords + w.leafwords + w.surfwords ) * 4 ) + 15 ) & ~(size_t)15;
+		w.vis_stage = 0;
+		if( need + rc_vis_tree_bytes( &sc ) <= budget )
+		{
+			w.vis_stage |= VW_STAGE_TREE; need += rc_vis_tree_bytes( &sc );
+			if( need + (size_t)w.stack_ints * 4 <= budget )
+			{
+				w.vis_stage |= VW_STAGE_SCRATCH; need += (size_t)w.stack_ints * 4;
+			}
+		}
+		w.vis_smem = (int32_t)need;
+	}
 
 	int k = 0;
 #define WALLOC( field, type, count ) do { type *p = nullptr; if( dalloc( &p, (size_t)( count )) != 0 ) return -1; w.field = p; D.d_work[k++] = p; } while( 0 )
@@ -373,7 +388,7 @@ int run_stages( bool timed )
 	CK( cudaMemsetAsync( D.d_nlist, 0, sizeof( int32_t ) * 2, st ));
 	CK( cudaMemsetAsync( w.bandcnt, 0, sizeof( int32_t ) * (size_t)w.nviews * w.nbands, st ));
 	if( timed ) CK( cudaEventRecord( D.ev[0], st ));
-	k_viswalk<<<w.nviews, VW_THREADS, sizeof( uint32_t ) * (size_t)(( w.visbytes_padded >> 2 ) + w.nodewords + w.leafwords + w.surfwords ), st>>>( sc, w ); D.launches++;
+	k_viswalk<<<w.nviews, VW_THREADS, (size_t)w.vis_smem, st>>>( sc, w ); D.launches++;
 	if( timed ) CK( cudaEventRecord( D.ev[1], st ));
 	{
 		dim3 g(( w.max_cands + 127 ) / 128, w.nviews );
@@ -418,6 +433,7 @@ int rc_dev_init( int device )
 	D.device = device;
 	CK( cudaStreamCreateWithFlags( &D.stream, cudaStreamNonBlocking ));
 	for( auto &e : D.ev ) CK( cudaEventCreate( &e ));
+	CK( cudaFuncSetAttribute( k_viswalk, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 64 ));
 	CK( cudaFuncSetAttribute( k_draw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_draw_smem(( 1920 + 7 ) / 8 + SC_SPCAP + 1 )));
 	for( int i = 0; i < 256; i++ ) D.h_styles[i] = 256;
 	if( upload( &D.d_styles, D.h_styles, 256 ) != 0 ) return -1;
@@ -485,7 +501,7 @@ int rc_dev_upload_scene( const rc_scene_t *sc, size_t cache_texels )
 
 	/* derived tables: every leaf's PVS row expanded once (Mod_DecompressPVS, engine/common/mod_bmodel.c:1054: zero
 	 * runs are {0, count} pairs), and the node each surface hangs off */
-	uint32_t *pvsdense = (uint32_t *)D.d_scene[11]; int32_t *surfnode = (int32_t *)D.d_scene[12];
+	uint32_t *pvsdense = (uint32_t *)D.d_scene[11]; int32_t *surfnode = (int32_t *)D.d_scene[12]; uint32_t *surfback = (uint32_t *)D.d_scene[13];
 	{
 		const int32_t vpad = ( sc->visbytes + 15 ) & ~15;
 		std::vector<uint8_t> dense((size_t)( sc->numleafs > 0 ? sc->numleafs : 1 ) * vpad, 0 );
@@ -513,9 +529,13 @@ int rc_dev_upload_scene( const rc_scene_t *sc, size_t cache_texels )
 				if( sc->nodes[n].firstsurface + k < sc->numsurfaces )
 					sn[sc->nodes[n].firstsurface + k] = n;
 		if( upload( &surfnode, sn.data(), sn.size()) != 0 ) return -1;
+		std::vector<uint32_t> sb((size_t)( sc->numsurfaces + 31 ) / 32 + 2, 0u );
+		for( int32_t i = 0; i < sc->numsurfaces; i++ )
+			if( sc->surfaces[i].flags & RC_SURF_PLANEBACK ) sb[i >> 5] |= 1u << ( i & 31 );
+		if( upload( &surfback, sb.data(), sb.size()) != 0 ) return -1;
 	}
-	D.d_scene[11] = pvsdense; D.d_scene[12] = surfnode;
-	d.pvsdense = pvsdense; d.surfnode = surfnode;
+	D.d_scene[11] = pvsdense; D.d_scene[12] = surfnode; D.d_scene[13] = surfback;
+	d.pvsdense = pvsdense; d.surfnode = surfnode; d.surfback = surfback;
 	D.d_scene[0] = planes; D.d_scene[1] = nodes; D.d_scene[2] = leafs; D.d_scene[3] = surfaces; D.d_scene[4] = marks;
 	D.d_scene[5] = surfedges; D.d_scene[6] = edges; D.d_scene[7] = verts; D.d_scene[8] = visdata; D.d_scene[9] = lightdata;
 	D.d_scene[10] = cache;

@@ -183,8 +183,16 @@ __global__ void __launch_bounds__( SP_THREADS ) k_spans( rc_work_t w )
 #ifdef RC_SPANS_DEBUG
 	__syncthreads();
 	DBG_MARK( dbg_t4 )
+	if( t < SP_LINES )
+	{
+		atomicAdd( &w.counters[24], (unsigned long long)s_cnt[t] ); atomicMax( &w.counters[25], (unsigned long long)s_cnt[t] );
+		if( s_cnt[t] > 32 ) atomicAdd( &w.counters[26], 1ull );
+		if( s_cnt[t] > 64 ) atomicAdd( &w.counters[27], 1ull );
+		if( s_cnt[t] > 128 ) atomicAdd( &w.counters[28], 1ull );
+	}
 	if( t == 0 )
 	{
+		atomicAdd( &w.counters[29], (unsigned long long)ne ); atomicMax( &w.counters[30], (unsigned long long)ne );
 		atomicAdd( &w.counters[16], (unsigned long long)( dbg_t1 - dbg_t0 )); atomicMax( &w.counters[17], (unsigned long long)( dbg_t1 - dbg_t0 ));
 		atomicAdd( &w.counters[18], (unsigned long long)( dbg_t2 - dbg_t1 )); atomicMax( &w.counters[19], (unsigned long long)( dbg_t2 - dbg_t1 ));
 		atomicAdd( &w.counters[20], (unsigned long long)( dbg_t3 - dbg_t2 )); atomicMax( &w.counters[21], (unsigned long long)( dbg_t3 - dbg_t2 ));

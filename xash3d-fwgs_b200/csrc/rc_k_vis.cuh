@@ -28,22 +28,46 @@
 #define VW_MAXLVL  1024
 #define VW_PVSCAP  32   /* leaves inside the fat-PVS radius handled by the parallel OR (r_pvs_radius is 0.1) */
 
-/* per-view int32 scratch: 6 arrays of cap entries + nodepos[numnodes] + leaf list[cap] */
+/* per-view int32 scratch: 8 arrays of cap entries (entries, sequence, leaf list, clipflags by position) + nodepos[numnodes] */
 static inline size_t rc_vis_scratch_ints( int32_t numnodes )
 {
 	const size_t cap = 2 * (size_t)numnodes + 2;
-	return 7 * cap + (size_t)numnodes + 8;
+	return 8 * cap + (size_t)numnodes + 8;
+}
+
+/* dynamic shared memory: bit sets, then (when they fit, w.vis_stage) a private copy of the BSP tree records and the
+ * per-view scratch - the walk is a chain of dependent loads, shared memory cuts every link from ~300 to ~30 cycles */
+#define VW_STAGE_TREE    1
+#define VW_STAGE_SCRATCH 2
+
+static inline size_t rc_vis_tree_bytes( const rc_scene_t *sc )
+{
+	return sizeof( rc_node_t ) * (size_t)sc->numnodes + sizeof( rc_plane_t ) * (size_t)sc->numplanes + sizeof( rc_leaf_t ) * (size_t)sc->numleafs;
+}
+
+__device__ __forceinline__ void rc_stage_copy( void *dst, const void *src, size_t bytes, int t )
+{
+	uint4 *d = reinterpret_cast<uint4 *>( dst );
+	const uint4 *s = reinterpret_cast<const uint4 *>( src );
+	for( size_t i = t; i < bytes / 16; i += VW_THREADS ) d[i] = s[i];
 }
 
 __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_work_t w )
 {
-	extern __shared__ uint32_t s_bits[];
+	extern __shared__ __align__( 16 ) uint32_t s_bits[];
 	__shared__ int32_t s_lvl[VW_MAXLVL + 2];
 	__shared__ int32_t s_n, s_nleaf, s_npvs, s_allvis, s_ovf;
 	__shared__ int32_t s_pvsleaf[VW_PVSCAP];
 	__shared__ int32_t s_warp[VW_THREADS / 32];
 
 	const int view = blockIdx.x, t = threadIdx.x, lane = t & 31, warp = t >> 5;
+#ifdef RC_SPANS_DEBUG
+	long long dbg_t[10]; int dbg_n = 0;
+#define VW_MARK() do { __syncthreads(); dbg_t[dbg_n++] = clock64(); } while( 0 )
+#else
+#define VW_MARK() do { } while( 0 )
+#endif
+	VW_MARK();
 	const rc_view_t *vw = &w.views[view];
 	const int32_t viswords = w.visbytes_padded >> 2;
 	uint32_t *vis = s_bits;
@@ -54,12 +78,29 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 
 	const int32_t cap = 2 * sc.numnodes + 2;
 	int32_t *scr = w.walkstack + (size_t)view * w.stack_ints;
+	{
+		unsigned char *p = reinterpret_cast<unsigned char *>( s_bits ) + (((size_t)allwords * 4 + 15 ) & ~(size_t)15 );
+		if( w.vis_stage & VW_STAGE_TREE )
+		{
+			rc_stage_copy( p, sc.nodes, sizeof( rc_node_t ) * (size_t)sc.numnodes, t );
+			sc.nodes = reinterpret_cast<const rc_node_t *>( p ); p += sizeof( rc_node_t ) * (size_t)sc.numnodes;
+			rc_stage_copy( p, sc.planes, sizeof( rc_plane_t ) * (size_t)sc.numplanes, t );
+			sc.planes = reinterpret_cast<const rc_plane_t *>( p ); p += sizeof( rc_plane_t ) * (size_t)sc.numplanes;
+			rc_stage_copy( p, sc.leafs, sizeof( rc_leaf_t ) * (size_t)sc.numleafs, t );
+			sc.leafs = reinterpret_cast<const rc_leaf_t *>( p ); p += sizeof( rc_leaf_t ) * (size_t)sc.numleafs;
+		}
+		if( w.vis_stage & VW_STAGE_SCRATCH )
+			scr = reinterpret_cast<int32_t *>( p );
+	}
 	int32_t *e_ref = scr, *e_info = scr + cap, *e_child = scr + 2 * (size_t)cap, *e_size = scr + 3 * (size_t)cap;
 	int32_t *e_pos = scr + 4 * (size_t)cap, *seq = scr + 5 * (size_t)cap, *leaflist = scr + 6 * (size_t)cap;
-	int32_t *nodepos = scr + 7 * (size_t)cap;
+	int32_t *posclip = scr + 7 * (size_t)cap;
+	int32_t *nodepos = scr + 8 * (size_t)cap;
 
 	for( int i = t; i < allwords; i += VW_THREADS ) s_bits[i] = 0;
 	for( int i = t; i < sc.numnodes; i += VW_THREADS ) nodepos[i] = -1; /* not visited: precedes no leaf */
+	__syncthreads();
+	VW_MARK(); /* 1: staged */
 	if( t == 0 )
 	{
 		s_n = 1; s_nleaf = 0; s_npvs = 0; s_allvis = 0; s_ovf = 0;
@@ -128,6 +169,7 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 	}
 	__syncthreads();
 
+	VW_MARK(); /* 2: fat pvs */
 	/* R_MarkLeaves: threads take clusters; a thread stops climbing where another one already passed */
 	for( int i = t; i < sc.numclusters; i += VW_THREADS )
 	{
@@ -145,6 +187,7 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 	}
 	__syncthreads();
 
+	VW_MARK(); /* 3: mark leaves */
 	/* P1: level-synchronous descent */
 	int32_t nlvl = 0;
 	if( t == 0 ) s_lvl[0] = 0;
@@ -198,6 +241,7 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 	}
 	__syncthreads();
 
+	VW_MARK(); /* 4: P1 */
 	/* P2: subtree sizes, deepest level first */
 	for( int32_t L = nlvl - 1; L >= 0; L-- )
 	{
@@ -215,6 +259,7 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 		__syncthreads();
 	}
 
+	VW_MARK(); /* 5: P2 */
 	/* P3: in-order positions */
 	if( t == 0 ) e_pos[0] = 0;
 	__syncthreads();
@@ -233,11 +278,13 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 				e_pos[c + 1] = mine + 1;
 				e_pos[e] = mine;
 				nodepos[e_ref[e]] = mine;
+				posclip[mine] = e_info[e] & 15;
 			}
 		}
 		__syncthreads();
 	}
 
+	VW_MARK(); /* 6: P3 */
 	/* P4: leaf marks that precede the surface's node */
 	{
 		const int32_t nleaf = s_nleaf;
@@ -257,30 +304,29 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 	}
 	__syncthreads();
 
-	/* P5: faces per visited node, laid out by in-order position */
-	const int32_t nseq = nlvl ? e_size[0] : 0, nent = s_n;
-	for( int32_t e = t; e < nent; e += VW_THREADS )
+	VW_MARK(); /* 7: P4 */
+	/* P5: the marked, viewer-facing surfaces are the candidates; their order is (in-order position of their
+	 * node, surface index).  Threads walk the set bits of the mark set: count per position, block prefix sum,
+	 * then every candidate lands at position base + its rank among the node's candidates. */
+	const int32_t nseq = nlvl ? e_size[0] : 0;
+	for( int32_t i = t; i < nseq; i += VW_THREADS ) seq[i] = 0;
+	__syncthreads();
+	for( int32_t wi = t; wi < w.surfwords; wi += VW_THREADS )
 	{
-		const int32_t info = e_info[e];
-		if( !( info & 16 ))
-			continue;
-		int32_t cnt = 0;
-		const int32_t ref = e_ref[e];
-		if( ref >= 0 )
+		uint32_t m = surfmark[wi];
+		while( m )
 		{
-			const rc_node_t *node = &sc.nodes[ref];
-			const int32_t c = node->numsurfaces;
-			if( c )
-			{
-				const double dot = rc_node_dot( vw, &sc.planes[node->plane] );
-				const int want = dot < -RC_BACKFACE_EPSILON ? 1 : ( dot > RC_BACKFACE_EPSILON ? 0 : -1 );
-				if( want >= 0 )
-					for( int32_t s = node->firstsurface; s < node->firstsurface + c; s++ )
-						if((( sc.surfaces[s].flags & RC_SURF_PLANEBACK ) ? 1 : 0 ) == want && rc_testbit( surfmark, s ))
-							cnt++;
-			}
+			const int32_t s = ( wi << 5 ) + __ffs( (int)m ) - 1;
+			m &= m - 1;
+			const int32_t n = sc.surfnode[s];
+			const double dot = rc_node_dot( vw, &sc.planes[sc.nodes[n].plane] );
+			const int want = dot < -RC_BACKFACE_EPSILON ? 1 : ( dot > RC_BACKFACE_EPSILON ? 0 : -1 );
+			const int back = ( sc.surfback[wi] >> ( s & 31 )) & 1;
+			if( back == want )
+				atomicAdd( &seq[nodepos[n]], 1 );
+			else
+				atomicAnd( &surfmark[wi], ~( 1u << ( s & 31 ))); /* marked but facing away: not a candidate */
 		}
-		seq[e_pos[e]] = cnt;
 	}
 	__syncthreads();
 	int32_t carry = 0;
@@ -303,32 +349,42 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 	}
 	const int32_t total = carry;
 	rc_cand_t *cands = w.cands + (size_t)view * w.max_cands;
-	for( int32_t e = t; e < nent; e += VW_THREADS )
+	for( int32_t wi = t; wi < w.surfwords; wi += VW_THREADS )
 	{
-		const int32_t info = e_info[e], ref = e_ref[e];
-		if( !( info & 16 ) || ref < 0 )
-			continue;
-		const rc_node_t *node = &sc.nodes[ref];
-		const int32_t c = node->numsurfaces;
-		if( !c )
-			continue;
-		const double dot = rc_node_dot( vw, &sc.planes[node->plane] );
-		const int want = dot < -RC_BACKFACE_EPSILON ? 1 : ( dot > RC_BACKFACE_EPSILON ? 0 : -1 );
-		if( want < 0 )
-			continue;
-		int32_t o = seq[e_pos[e]];
-		for( int32_t s = node->firstsurface; s < node->firstsurface + c; s++ )
-			if((( sc.surfaces[s].flags & RC_SURF_PLANEBACK ) ? 1 : 0 ) == want && rc_testbit( surfmark, s ))
+		uint32_t m = surfmark[wi];
+		while( m )
+		{
+			const int32_t b = __ffs( (int)m ) - 1, s = ( wi << 5 ) + b;
+			m &= m - 1;
+			const int32_t n = sc.surfnode[s], pos = nodepos[n];
+			/* rank among the node's candidates: surviving marks in [firstsurface, s) */
+			const int32_t f = sc.nodes[n].firstsurface;
+			int32_t rank = 0;
+			for( int32_t k = f >> 5; k <= wi; k++ )
 			{
-				if( o < w.max_cands )
-				{
-					cands[o].surf = s;
-					cands[o].clipflags = info & 15;
-				}
-				o++;
+				uint32_t mk = surfmark[k];
+				if( k == ( f >> 5 )) mk &= ~0u << ( f & 31 );
+				if( k == wi ) mk &= ( 1u << b ) - 1u;
+				rank += __popc( mk );
 			}
+			const int32_t o = seq[pos] + rank;
+			if( o < w.max_cands )
+			{
+				cands[o].surf = s;
+				cands[o].clipflags = posclip[pos];
+			}
+		}
 	}
 
+	VW_MARK(); /* 8: P5 */
+#ifdef RC_SPANS_DEBUG
+	if( t == 0 )
+		for( int k = 0; k < 8; k++ )
+		{
+			atomicAdd( &w.counters[32 + 2 * k], (unsigned long long)( dbg_t[k + 1] - dbg_t[k] ));
+			atomicMax( &w.counters[33 + 2 * k], (unsigned long long)( dbg_t[k + 1] - dbg_t[k] ));
+		}
+#endif
 	if( t == 0 )
 	{
 		w.ncands[view] = total < w.max_cands ? total : w.max_cands;

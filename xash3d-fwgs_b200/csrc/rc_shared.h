@@ -108,6 +108,7 @@ typedef struct
 	/* derived on upload (rc_dev_upload_scene); host callers leave them NULL */
 	const uint32_t     *pvsdense;  /* [numleafs][visbytes_padded / 4] Mod_DecompressPVS of every leaf's row */
 	const int32_t      *surfnode;  /* [numsurfaces] the node a surface hangs off */
+	const uint32_t     *surfback;  /* [numsurfaces bits] SURF_PLANEBACK */
 } rc_scene_t;
 
 /* per-view constants: everything R_SetupFrustum/R_SetupFrameQ/R_ViewChanged/R_TransformFrustum derive
@@ -192,7 +193,7 @@ enum
 {
 	RC_CTR_VIEWS = 0, RC_CTR_PIXELS, RC_CTR_CANDS, RC_CTR_SURFS, RC_CTR_EDGES, RC_CTR_SPANS,
 	RC_CTR_CACHE_BLOCKS, RC_CTR_CACHE_TEXELS, RC_CTR_OVERFLOW_EDGES, RC_CTR_OVERFLOW_EVENTS,
-	RC_CTR_OVERFLOW_STACK, RC_CTR_OVERFLOW_CANDS, RC_CTR_COUNT = 32
+	RC_CTR_OVERFLOW_STACK, RC_CTR_OVERFLOW_CANDS, RC_CTR_COUNT = 64 /* 16.. = debug-build phase clocks */
 };
 
 #ifdef __cplusplus
