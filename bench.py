@@ -13,7 +13,7 @@ and the counters).
            L2 flushed between steps, max over ranks)
   e2e    = the same through the plugin's public C-ABI call RefCuda_RenderViews with HOST buffers: view
            descriptors go host->device and the colour frames come back device->host (pinned) every step
-  roofline = the span kernel (k_scanlines): 6 algorithmic bytes per pixel / its CUDA-event time vs the
+  roofline = the span drawing kernel (k_draw): 6 algorithmic bytes per pixel / its CUDA-event time vs the
            measured HBM copy bandwidth (MEASURED_PEAKS.json)
   cpu_baseline = the oracle (unmodified ref_soft, oracle/_ref) timed on one host core on a bounded sample
 """
@@ -75,7 +75,7 @@ def measured_traffic():
     p = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(p):
         try:
-            return json.load(open(p)).get("k_scanlines_dram_bytes_per_launch")
+            return json.load(open(p)).get("k_draw_dram_bytes_per_launch")
         except Exception:
             return None
     return None
@@ -296,7 +296,7 @@ def run_cuda(args):
     launches = r.launch_count() - l0
     barrier()
     ms_step = allmax(ms)
-    ms_scan = allmax(stages[3])
+    ms_scan = allmax(stages[4])
 
     # -- e2e: the public C-ABI call with host buffers (H2D view descriptors, D2H colour frames), wall clock
     for _ in range(max(args.warmup, 3)):
@@ -326,11 +326,11 @@ def run_cuda(args):
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "int32/f32 (16-bit pixel_t)", "data": "synthetic", "config": workload(args, world),
             "frames_per_s": n * world / (ms_step * 1e-3),
-            "stage_ms": {"vis_walk": stages[0], "faces_edges": stages[1], "surface_cache": stages[2], "scanlines": stages[3]},
+            "stage_ms": {"vis_walk": stages[0], "faces_edges": stages[1], "surface_cache": stages[2], "spans": stages[3], "draw": stages[4]},
             "e2e": {"value": total_px / e2e_s / 1e6, "unit": UNIT, "h2d_bytes_per_step": n * 56, "d2h_bytes_per_step": px * 2,
                     "ms_per_step": e2e_s * 1e3, "note": "RefCuda_RenderViews: ref_viewpass_t array in, colour frames out to pinned host memory"},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "k_scanlines", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "roofline": {"bound": "hbm", "kernel": "k_draw", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": measured_traffic(), "algorithmic_bytes_per_launch": BYTES_PER_PIXEL * px, "peak_source": peak_src,
                          "kernel_ms": ms_scan},
             "clocks": clocks, "counters": counters, "device": r.device_name(),

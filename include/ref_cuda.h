@@ -40,7 +40,8 @@ REF_CUDA_EXPORT int GetRefAPI( int version, struct ref_interface_s *pFunctionTab
 REF_CUDA_EXPORT int RefCuda_RenderViews( const struct ref_viewpass_s *views, int nviews, unsigned short *color_out, short *z_out, int clear );
 
 /* Re-run the device stages of the last batch with all inputs resident in HBM; CUDA-event milliseconds
- * per iteration: total and per stage [visibility+BSP walk, face/edge set-up, surface cache, scanlines].
+ * per iteration: total and per stage, ms_stage[5] = [visibility+BSP walk, face/edge set-up, surface cache,
+ * span generation, span drawing].
  * flags: 1 = invalidate the surface cache before every iteration, 2 = flush L2 (256 MB write) between
  * iterations, outside the timed region. */
 REF_CUDA_EXPORT int RefCuda_BenchResident( int iters, int flags, float *ms_total, float *ms_stage );

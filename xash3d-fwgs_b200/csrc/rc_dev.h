@@ -40,10 +40,11 @@ int rc_dev_flush_cache( void );
 int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, int clear, uint16_t *color_out, int16_t *z_out );
 
 /* re-run the device stages of the last rc_dev_render batch (inputs resident in HBM) 'iters' times and
- * report CUDA-event milliseconds: total and per stage (vis+walk, faces, cache, scan) */
+ * report CUDA-event milliseconds: total and per stage (vis+walk, faces, cache, spans, draw) */
 #define RC_BENCH_REBUILD_CACHE 1 /* invalidate every cache block before each iteration (config C3 behaviour) */
 #define RC_BENCH_FLUSH_L2      2 /* write 256 MB between iterations, outside the timed region */
-int rc_dev_bench_resident( int iters, int flags, float *ms_total, float *ms_stage /* [4] */ );
+#define RC_BENCH_STAGES        5 /* vis+walk, faces, cache, spans, draw */
+int rc_dev_bench_resident( int iters, int flags, float *ms_total, float *ms_stage /* [RC_BENCH_STAGES] */ );
 
 /* probes for the parity tests */
 int rc_dev_read_cache_block( int surf, int mip, uint16_t *out, int maxtexels, int *width, int *height, int *valid );

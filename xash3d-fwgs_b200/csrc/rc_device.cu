@@ -7,7 +7,7 @@
  *   S1 k_faces        R_RenderFace/R_ClipEdge/R_EmitEdge + D_CalcGradients             one thread per (view, face)
  *   S2 k_cache_list   D_CacheSurface staleness test -> work list                        one thread per (face, mip)
  *      k_cache_build  R_BuildLightMap + R_DrawSurface                                   persistent CTAs, one block per (face, mip)
- *   S3 k_spans        R_ScanEdges/R_GenerateSpans (rc_k_spans.cuh)                      one thread per (view, scanline)
+ *   S3 k_events/k_lines R_ScanEdges/R_GenerateSpans (rc_k_spans.cuh)                    lane per scanline / warp per scanline
  *      k_draw         D_DrawSpans16/D_DrawZSpans/Turbulent8/D_BackgroundSurf (rc_k_draw.cuh) one warp per (view, scanline)
  *
  * The per-item arithmetic is rc_core.h (shared with the CPU debug harness); this file is the parallel
@@ -67,7 +67,8 @@ struct rc_work_t
 	unsigned long long *counters;
 };
 
-#define SP_LINES 64 /* scanlines per band (rc_k_spans.cuh): k_faces bins edges by band */
+#define SP_LINES 32 /* scanlines per band (rc_k_spans.cuh): k_faces bins edges by band */
+#define LN_GRID  ( 148 * 12 ) /* k_lines blocks: 12 resident blocks of 4 warps per SM */
 #define CACHE_THREADS 256
 #define CACHE_LUXCAP 2048
 
@@ -357,7 +358,7 @@ int ensure_batch( int nviews, int width, int height )
 	w.view_events = (size_t)w.nbands * w.blk_events;
 	w.scanbits = nullptr; w.scanbits_words = ( w.max_cands + 32 ) / 32;
 	if( w.scanbits_words > SP_BITWORDS )
-		WALLOC( scanbits, uint32_t, (size_t)cap * w.nbands * SP_LINES * w.scanbits_words );
+		WALLOC( scanbits, uint32_t, (size_t)LN_GRID * LN_WARPS * w.scanbits_words );
 	WALLOC( bandcnt, int32_t, (size_t)cap * w.nbands );
 	WALLOC( bandedges, rc_edge_t, (size_t)cap * w.nbands * w.band_cap );
 	WALLOC( events, unsigned long long, (size_t)cap * w.view_events );
@@ -403,12 +404,16 @@ int run_stages( bool timed )
 	if( timed ) CK( cudaEventRecord( D.ev[3], st ));
 	{
 		dim3 g( w.nbands, w.nviews );
-		k_spans<<<g, SP_THREADS, 0, st>>>( w ); D.launches++;
+		k_events<<<g, EV_THREADS, 0, st>>>( w ); D.launches++;
+		const int nlines = w.nviews * w.height;
+		const int lblocks = ( nlines + LN_WARPS - 1 ) / LN_WARPS;
+		k_lines<<<lblocks < LN_GRID ? lblocks : LN_GRID, LN_WARPS * 32, 0, st>>>( w ); D.launches++;
+		if( timed ) CK( cudaEventRecord( D.ev[4], st ));
 		const int32_t chunkcap = ( w.width + 7 ) / 8 + SC_SPCAP + 1;
 		dim3 g2(( w.height + DR_WARPS - 1 ) / DR_WARPS, w.nviews );
 		k_draw<<<g2, DR_WARPS * 32, rc_draw_smem( chunkcap ), st>>>( sc, w, chunkcap ); D.launches++;
 	}
-	if( timed ) CK( cudaEventRecord( D.ev[4], st ));
+	if( timed ) CK( cudaEventRecord( D.ev[5], st ));
 	CK( cudaGetLastError());
 	return 0;
 }
@@ -618,7 +623,7 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 int rc_dev_bench_resident( int iters, int flags, float *ms_total, float *ms_stage )
 {
 	if( !D.have_batch ) { snprintf( D.err, sizeof( D.err ), "no batch rendered yet" ); return -1; }
-	float tot = 0, stage[4] = { 0, 0, 0, 0 };
+	float tot = 0, stage[RC_BENCH_STAGES] = { 0 };
 	const size_t flush_bytes = (size_t)256 << 20; /* > 126 MB of L2 */
 	if(( flags & RC_BENCH_FLUSH_L2 ) && !D.d_flush )
 		CK( cudaMalloc( &D.d_flush, flush_bytes ));
@@ -631,11 +636,11 @@ int rc_dev_bench_resident( int iters, int flags, float *ms_total, float *ms_stag
 		if( run_stages( true ) != 0 ) return -1;
 		CK( cudaStreamSynchronize( D.stream ));
 		float ms;
-		CK( cudaEventElapsedTime( &ms, D.ev[0], D.ev[4] )); tot += ms;
-		for( int s = 0; s < 4; s++ ) { CK( cudaEventElapsedTime( &ms, D.ev[s], D.ev[s + 1] )); stage[s] += ms; }
+		CK( cudaEventElapsedTime( &ms, D.ev[0], D.ev[RC_BENCH_STAGES] )); tot += ms;
+		for( int s = 0; s < RC_BENCH_STAGES; s++ ) { CK( cudaEventElapsedTime( &ms, D.ev[s], D.ev[s + 1] )); stage[s] += ms; }
 	}
 	if( ms_total ) *ms_total = tot / ( iters > 0 ? iters : 1 );
-	if( ms_stage ) for( int s = 0; s < 4; s++ ) ms_stage[s] = stage[s] / ( iters > 0 ? iters : 1 );
+	if( ms_stage ) for( int s = 0; s < RC_BENCH_STAGES; s++ ) ms_stage[s] = stage[s] / ( iters > 0 ? iters : 1 );
 	return 0;
 }
 

@@ -133,9 +133,9 @@ class Renderer:
             raise RuntimeError("RefCuda_RenderViews failed")
 
     def bench_resident(self, iters, rebuild_cache=False, flush_l2=False):
-        """CUDA-event ms per iteration of the last batch re-run with inputs resident in HBM: (total, [4 stages])."""
+        """CUDA-event ms per iteration of the last batch re-run with inputs resident in HBM: (total, [5 stages: vis_walk, faces_edges, surface_cache, spans, draw])."""
         tot = C.c_float()
-        st = (C.c_float * 4)()
+        st = (C.c_float * 5)()
         if self._bench(iters, (1 if rebuild_cache else 0) | (2 if flush_l2 else 0), C.byref(tot), st) != 0:
             raise RuntimeError("RefCuda_BenchResident failed")
         return tot.value, list(st)
