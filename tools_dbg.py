@@ -7,9 +7,9 @@ cu = scene.Renderer(pkg.REF_CUDA_PATH, 320, 240, m)
 cu.render_views(m.cameras[:256])
 cu.render_views(m.cameras[:256])
 a = np.zeros(64, np.uint64); cu._counters(a.ctypes.data, 64)
-for i, name in enumerate(['count', 'fill', 'sort', 'replay']):
-    print(name, 'mean cycles/block', int(a[16 + 2 * i]) / 1024, 'max', int(a[17 + 2 * i]))
-print('events total', int(a[24]), 'max/line', int(a[25]), 'lines >32', int(a[26]), '>64', int(a[27]), '>128', int(a[28]), 'band edges total', int(a[29]), 'max', int(a[30]))
+nl = int(a[20])
+print('lines', nl, 'sort mean cycles/line', int(a[16]) / nl, 'max', int(a[17]), 'replay mean', int(a[18]) / nl, 'max', int(a[19]), 'warp total max cycles', int(a[21]))
+print('events total', int(a[24]), 'max/line', int(a[25]))
 print(cu.counters())
 for i, name in enumerate(['stage', 'fatpvs', 'markleaves', 'P1', 'P2', 'P3', 'P4', 'P5']):
     print('vis', name, 'mean cycles/block', int(a[32 + 2 * i]) / 256, 'max', int(a[33 + 2 * i]))

@@ -602,7 +602,10 @@ RC_HD int rc_edge_active( const rc_edge_t *e, int32_t y )
  * screen border or for the two copies of a shared edge) broken so that the result is deterministic */
 RC_HD uint64_t rc_event_key( int32_t u, uint32_t surfs )
 {
-	return ((uint64_t)((uint32_t)u ^ 0x80000000u ) << 32 ) | surfs;
+	/* low word: leading surface in bits 0..15, trailing surface in bits 16..31 (the halves of rc_edge_t.surfs
+	 * swapped) - at equal u a leading edge sorts in front of a trailing edge, the order R_EmitEdge's sorted insert
+	 * gives new edges (u_check++ for trailing edges, ref/soft/r_rast.c:233-235) */
+	return ((uint64_t)((uint32_t)u ^ 0x80000000u ) << 32 ) | ( surfs >> 16 ) | ( surfs << 16 );
 }
 
 /*
@@ -723,7 +726,7 @@ RC_HD int32_t rc_generate_spans_bits( const unsigned long long *keys, int32_t ne
 		if( u > tail_u )
 			break;
 		const int32_t iu = u >> 20;
-		const int32_t trail = (int32_t)( both & 0xFFFF ), lead = (int32_t)( both >> 16 );
+		const int32_t trail = (int32_t)( both >> 16 ), lead = (int32_t)( both & 0xFFFF );
 
 		if( trail )
 		{

@@ -111,6 +111,115 @@ __device__ __forceinline__ void rc_sort_smem( unsigned long long *buf, int32_t n
 		}
 }
 
+/*
+ * R_GenerateSpans for one scanline by a whole warp, lane per event (32 sorted events per round).
+ *
+ * What the serial replay (rc_generate_spans_bits) carries from event to event is the set of surfaces on the
+ * stack; with spanstate in {0, 1} a leading edge sets its surface's bit and a trailing edge clears it, i.e. both
+ * TOGGLE it, so the set after event i is the XOR of the toggles of events 0..i: one inclusive XOR scan over the
+ * lanes (NW words of bit set per lane, 5 shuffle steps each).  From the set after every event: the top surface
+ * (lowest set bit = smallest key), the top before it (neighbour lane), whether the event ends a span (trailing
+ * edge of the top / leading edge in front of the top), the start of that span (running max of the pixel column
+ * of earlier span ends) - and the spans are compacted out with a ballot.  A leading edge that finds its bit set,
+ * or a trailing edge that finds it clear (spanstate outside {0, 1}: inverted or doubled spans), makes the warp
+ * give the line to the serial replay instead.  Returns the span count, or -1 for "replay serially".
+ */
+template <int NW>
+__device__ __forceinline__ int32_t rc_replay_warp( const unsigned long long *keys, int32_t n, int32_t head_iu, int32_t tail_u,
+	rc_span_t *spans, int lane )
+{
+	uint32_t st[NW];
+#pragma unroll
+	for( int k = 0; k < NW; k++ ) st[k] = 0;
+	int32_t top_carry = 0, last_u = head_iu, nspans = 0;
+	const uint32_t lt = ( 1u << lane ) - 1u;
+
+	for( int32_t c0 = 0; c0 < n; c0 += 32 )
+	{
+		const int32_t i = c0 + lane;
+		const unsigned long long key = i < n ? keys[i] : 0ull;
+		const int32_t u = (int32_t)((uint32_t)( key >> 32 ) ^ 0x80000000u );
+		const uint32_t both = (uint32_t)key;
+		const bool valid = i < n && u <= tail_u;
+		const int32_t iu = u >> 20;
+		const uint32_t trail = both >> 16, lead = both & 0xFFFFu;
+		const bool is_lead = lead != 0;
+		const int32_t s = (int32_t)( is_lead ? lead : trail );
+		const uint32_t bit = 1u << ( s & 31 );
+		const int32_t wsel = s >> 5;
+		bool exc = valid && (( trail != 0 && lead != 0 ) || wsel >= NW );
+
+		uint32_t x[NW];
+#pragma unroll
+		for( int k = 0; k < NW; k++ ) x[k] = ( valid && wsel == k ) ? bit : 0u;
+#pragma unroll
+		for( int d = 1; d < 32; d <<= 1 )
+		{
+#pragma unroll
+			for( int k = 0; k < NW; k++ )
+			{
+				const uint32_t o = __shfl_up_sync( 0xFFFFFFFFu, x[k], d );
+				if( lane >= d ) x[k] ^= o;
+			}
+		}
+		uint32_t mine = 0;
+		int32_t top_after = 0;
+#pragma unroll
+		for( int k = NW - 1; k >= 0; k-- )
+		{
+			x[k] ^= st[k]; /* the set after this lane's event */
+			if( wsel == k ) mine = x[k];
+			if( x[k] ) top_after = ( k << 5 ) + __ffs( (int)x[k] ) - 1;
+		}
+		/* leading edge: the bit must have been clear (now set); trailing edge: set (now clear) */
+		exc = exc || ( valid && ((( mine & bit ) != 0 ) != is_lead ));
+		if( __ballot_sync( 0xFFFFFFFFu, exc ))
+			return -1;
+
+		int32_t top_before = __shfl_up_sync( 0xFFFFFFFFu, top_after, 1 );
+		if( lane == 0 ) top_before = top_carry;
+		const bool brk = valid && ( is_lead ? ( top_before == 0 || s < top_before ) : ( s == top_before ));
+
+		/* pixel column of the latest span end before this event */
+		int32_t m = brk ? iu : (int32_t)0x80000000;
+#pragma unroll
+		for( int d = 1; d < 32; d <<= 1 )
+		{
+			const int32_t o = __shfl_up_sync( 0xFFFFFFFFu, m, d );
+			if( lane >= d && o > m ) m = o;
+		}
+		int32_t prev = __shfl_up_sync( 0xFFFFFFFFu, m, 1 );
+		if( lane == 0 || prev < last_u ) prev = last_u;
+		const bool emit = brk && iu > prev;
+		const uint32_t em = __ballot_sync( 0xFFFFFFFFu, emit );
+		if( emit )
+		{
+			rc_span_t sp;
+			sp.surf = top_before; sp.u = (int16_t)prev; sp.count = (int16_t)( iu - prev );
+			spans[nspans + __popc( em & lt )] = sp;
+		}
+		nspans += __popc( em );
+#pragma unroll
+		for( int k = 0; k < NW; k++ ) st[k] = __shfl_sync( 0xFFFFFFFFu, x[k], 31 );
+		top_carry = __shfl_sync( 0xFFFFFFFFu, top_after, 31 );
+		const int32_t mlast = __shfl_sync( 0xFFFFFFFFu, m, 31 );
+		if( mlast > last_u ) last_u = mlast;
+	}
+	/* R_CleanupSpan: whatever is on top runs to the right edge */
+	const int32_t iu = tail_u >> 20;
+	if( iu > last_u )
+	{
+		if( lane == 0 )
+		{
+			rc_span_t sp;
+			sp.surf = top_carry; sp.u = (int16_t)last_u; sp.count = (int16_t)( iu - last_u );
+			spans[nspans] = sp;
+		}
+		nspans++;
+	}
+	return nspans;
+}
+
 __global__ void __launch_bounds__( LN_WARPS * 32 ) k_lines( rc_work_t w )
 {
 	__shared__ __align__( 16 ) unsigned long long s_keys[LN_WARPS][SP_SORTCAP];
@@ -120,7 +229,10 @@ __global__ void __launch_bounds__( LN_WARPS * 32 ) k_lines( rc_work_t w )
 	const int32_t gwarp = blockIdx.x * LN_WARPS + warp, nwarps = gridDim.x * LN_WARPS;
 	const int32_t nlines = w.nviews * w.height;
 	unsigned long long *keys = s_keys[warp];
-	int32_t nspans_total = 0, novf = 0;
+	int32_t nspans_total = 0, novf = 0, nserial = 0;
+#ifdef RC_SPANS_DEBUG
+	const long long dbg_start = clock64();
+#endif
 
 	for( int32_t line = gwarp; line < nlines; line += nwarps )
 	{
@@ -131,6 +243,9 @@ __global__ void __launch_bounds__( LN_WARPS * 32 ) k_lines( rc_work_t w )
 		const rc_view_t *vw = &w.views[view];
 		const int32_t x0 = vw->vrect[0], vw_w = vw->vrect[2];
 		const int32_t n = li.nsp;
+#ifdef RC_SPANS_DEBUG
+		const long long dbg0 = clock64();
+#endif
 		unsigned long long *slice = w.events + (size_t)view * w.view_events + li.ofs;
 		const unsigned long long *sorted = keys;
 
@@ -168,29 +283,67 @@ __global__ void __launch_bounds__( LN_WARPS * 32 ) k_lines( rc_work_t w )
 			sorted = slice;
 		}
 
+#ifdef RC_SPANS_DEBUG
+		__syncwarp();
+		const long long dbg1 = clock64();
+#endif
 		const int32_t nwords = ( w.ncands[view] + 32 ) >> 5;
 		uint32_t *bits = s_bits[warp];
 		if( nwords > SP_BITWORDS )
 			bits = w.scanbits + (size_t)gwarp * (size_t)w.scanbits_words;
-		for( int32_t k = lane; k < nwords; k += 32 ) bits[k] = 0;
 		__syncwarp();
 
+		int32_t nsp = -1;
+		const int32_t tail_u = (( x0 + vw_w ) << 20 ) + 0xFFFFF;
+		if( sorted == keys )
+		{
+			/* invalid lanes of a partial round read keys[i >= n]: harmless (never used) */
+			if( nwords <= 2 ) nsp = rc_replay_warp<2>( keys, n, x0, tail_u, reinterpret_cast<rc_span_t *>( slice ), lane );
+			else if( nwords <= 4 ) nsp = rc_replay_warp<4>( keys, n, x0, tail_u, reinterpret_cast<rc_span_t *>( slice ), lane );
+			else if( nwords <= 8 ) nsp = rc_replay_warp<8>( keys, n, x0, tail_u, reinterpret_cast<rc_span_t *>( slice ), lane );
+			else if( nwords <= 16 ) nsp = rc_replay_warp<16>( keys, n, x0, tail_u, reinterpret_cast<rc_span_t *>( slice ), lane );
+		}
+		if( nsp < 0 )
+		{
+			/* degenerate line (or a view listing more faces than the register bit set holds): serial replay */
+			for( int32_t k = lane; k < nwords; k += 32 ) bits[k] = 0;
+			__syncwarp();
+			if( lane == 0 )
+			{
+				int32_t exc[2 * SP_EXCCAP];
+				int32_t ovf = 0;
+				nsp = rc_generate_spans_bits( sorted, n, x0, tail_u, bits, nwords, exc, SP_EXCCAP,
+					reinterpret_cast<rc_span_t *>( slice ), n + 1, &ovf );
+				novf += ovf;
+				nserial++;
+			}
+			nsp = __shfl_sync( 0xFFFFFFFFu, nsp, 0 );
+		}
 		if( lane == 0 )
 		{
-			int32_t exc[2 * SP_EXCCAP];
-			int32_t ovf = 0;
-			const int32_t nsp = rc_generate_spans_bits( sorted, n, x0, (( x0 + vw_w ) << 20 ) + 0xFFFFF, bits, nwords, exc, SP_EXCCAP,
-				reinterpret_cast<rc_span_t *>( slice ), n + 1, &ovf );
 			w.lineinfo[line].nsp = nsp;
 			nspans_total += nsp;
-			novf += ovf;
 		}
 		__syncwarp();
+#ifdef RC_SPANS_DEBUG
+		if( lane == 0 )
+		{
+			const long long dbg2 = clock64();
+			atomicAdd( &w.counters[16], (unsigned long long)( dbg1 - dbg0 )); atomicMax( &w.counters[17], (unsigned long long)( dbg1 - dbg0 ));
+			atomicAdd( &w.counters[18], (unsigned long long)( dbg2 - dbg1 )); atomicMax( &w.counters[19], (unsigned long long)( dbg2 - dbg1 ));
+			atomicAdd( &w.counters[24], (unsigned long long)n ); atomicMax( &w.counters[25], (unsigned long long)n );
+			atomicAdd( &w.counters[20], 1ull );
+		}
+#endif
 	}
+#ifdef RC_SPANS_DEBUG
+	if( lane == 0 ) atomicMax( &w.counters[21], (unsigned long long)( clock64() - dbg_start ));
+#endif
 	if( lane == 0 )
 	{
 		if( nspans_total ) atomicAdd( &w.counters[RC_CTR_SPANS], (unsigned long long)nspans_total );
 		if( novf ) atomicAdd( &w.counters[RC_CTR_OVERFLOW_EVENTS], (unsigned long long)novf );
+		if( nserial ) atomicAdd( &w.counters[RC_CTR_SERIAL_LINES], (unsigned long long)nserial );
 	}
 }
 
