@@ -58,6 +58,8 @@ struct rc_work_t
 	int32_t    scanbits_words, nbands;
 	int32_t   *bandcnt;   /* [nviews][nbands] edges binned per band of SP_LINES scanlines */
 	rc_edge_t *bandedges; /* [nviews][nbands][band_cap] */
+	uint16_t  *bandsurf;  /* [nviews][nbands][band_cap + 2] band-local surface number -> candidate index + 1 */
+	int32_t   *bandnloc;  /* [nviews][nbands] surfaces present in the band */
 	int32_t    band_cap, blk_events; /* capacities: edges per band, event/span slots per band */
 	size_t     view_events;          /* nbands * blk_events */
 	unsigned long long *events;      /* [nviews][nbands][blk_events] sort keys, then rc_span_t in place */
@@ -361,6 +363,8 @@ int ensure_batch( int nviews, int width, int height )
 		WALLOC( scanbits, uint32_t, (size_t)LN_GRID * LN_WARPS * w.scanbits_words );
 	WALLOC( bandcnt, int32_t, (size_t)cap * w.nbands );
 	WALLOC( bandedges, rc_edge_t, (size_t)cap * w.nbands * w.band_cap );
+	WALLOC( bandsurf, uint16_t, (size_t)cap * w.nbands * ( (size_t)w.band_cap + 2 ));
+	WALLOC( bandnloc, int32_t, (size_t)cap * w.nbands );
 	WALLOC( events, unsigned long long, (size_t)cap * w.view_events );
 	WALLOC( lineinfo, rc_lineinfo_t, (size_t)cap * height );
 	WALLOC( color, uint16_t, (size_t)cap * width * height );
@@ -404,7 +408,7 @@ int run_stages( bool timed )
 	if( timed ) CK( cudaEventRecord( D.ev[3], st ));
 	{
 		dim3 g( w.nbands, w.nviews );
-		k_events<<<g, EV_THREADS, 0, st>>>( w ); D.launches++;
+		k_events<<<g, EV_THREADS, rc_events_smem( w.scanbits_words ), st>>>( w ); D.launches++;
 		const int nlines = w.nviews * w.height;
 		const int lblocks = ( nlines + LN_WARPS - 1 ) / LN_WARPS;
 		k_lines<<<lblocks < LN_GRID ? lblocks : LN_GRID, LN_WARPS * 32, 0, st>>>( w ); D.launches++;
@@ -439,6 +443,7 @@ int rc_dev_init( int device )
 	CK( cudaStreamCreateWithFlags( &D.stream, cudaStreamNonBlocking ));
 	for( auto &e : D.ev ) CK( cudaEventCreate( &e ));
 	CK( cudaFuncSetAttribute( k_viswalk, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 64 ));
+	CK( cudaFuncSetAttribute( k_events, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_events_smem( 65536 / 32 + 2 )));
 	CK( cudaFuncSetAttribute( k_draw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_draw_smem(( 1920 + 7 ) / 8 + SC_SPCAP + 1 )));
 	for( int i = 0; i < 256; i++ ) D.h_styles[i] = 256;
 	if( upload( &D.d_styles, D.h_styles, 256 ) != 0 ) return -1;

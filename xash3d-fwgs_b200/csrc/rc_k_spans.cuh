@@ -31,9 +31,21 @@
 #error "k_events maps lanes to scanlines: SP_LINES must be 32"
 #endif
 
+#define EV_ECAP 2048 /* band edges staged and pre-sorted in shared memory; longer lists are read from HBM unsorted */
+
+static inline size_t rc_events_smem( int32_t bitwords )
+{
+	return sizeof( rc_edge_t ) * EV_ECAP + sizeof( unsigned long long ) * EV_ECAP + sizeof( uint32_t ) * 2 * ( (size_t)bitwords + 1 );
+}
+
 __global__ void __launch_bounds__( EV_THREADS ) k_events( rc_work_t w )
 {
+	extern __shared__ __align__( 16 ) unsigned char ev_smem[];
 	__shared__ int32_t s_wcnt[EV_WARPS][SP_LINES];
+	__shared__ int32_t s_warp[EV_WARPS];
+	rc_edge_t *s_edge = reinterpret_cast<rc_edge_t *>( ev_smem );
+	unsigned long long *s_key = reinterpret_cast<unsigned long long *>( ev_smem + sizeof( rc_edge_t ) * EV_ECAP );
+	uint32_t *s_bm = reinterpret_cast<uint32_t *>( ev_smem + ( sizeof( rc_edge_t ) + sizeof( unsigned long long )) * EV_ECAP );
 
 	const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
 	const int band = blockIdx.x, view = blockIdx.y, nbands = gridDim.x;
@@ -46,12 +58,95 @@ __global__ void __launch_bounds__( EV_THREADS ) k_events( rc_work_t w )
 	if( ne > w.band_cap ) ne = w.band_cap;
 	const rc_edge_t *gedges = w.bandedges + ((size_t)view * nbands + band ) * w.band_cap;
 	unsigned long long *arena = w.events + ((size_t)view * nbands + band ) * w.blk_events;
+	const int32_t bmwords = ( w.ncands[view] + 32 ) >> 5; /* surface numbers are candidate index + 1 */
+	uint32_t *s_pre = s_bm + bmwords;
 
-	/* 1. events per line: this warp's share of the edges */
-	int32_t cnt = 0;
-	for( int32_t k = warp; k < ne; k += EV_WARPS )
+	/* A. stage the band's edges, mark the surfaces they belong to, sort keys = u at the band's middle line
+	 * (taken at the nearest line the edge is active on) */
+	const bool staged = ne <= EV_ECAP;
+	const rc_edge_t *E = staged ? s_edge : gedges;
+	for( int32_t i = t; i < bmwords; i += EV_THREADS ) s_bm[i] = 0;
+	__syncthreads();
+	int32_t npow = 32;
+	while( npow < ne ) npow <<= 1;
+	const int32_t ymid = band * SP_LINES + SP_LINES / 2;
+	for( int32_t k = t; k < ( staged ? npow : ne ); k += EV_THREADS )
 	{
-		const uint32_t vv = gedges[k].vv;
+		if( k >= ne ) { s_key[k] = ~0ull; continue; }
+		const rc_edge_t e = gedges[k];
+		const int32_t s = (int32_t)(( e.surfs & 0xFFFF ) ? ( e.surfs & 0xFFFF ) : ( e.surfs >> 16 ));
+		atomicOr( &s_bm[s >> 5], 1u << ( s & 31 ));
+		if( staged )
+		{
+			s_edge[k] = e;
+			const int32_t v = (int32_t)( e.vv & 0xFFFF ), v2 = (int32_t)( e.vv >> 16 );
+			const int32_t ym = ymid < v ? v : ( ymid > v2 ? v2 : ymid );
+			const uint32_t um = (uint32_t)e.u + (uint32_t)( ym - v ) * (uint32_t)e.u_step;
+			/* ties (the two copies of a shared edge) in the order the event keys will have: leading first, then by surface */
+			s_key[k] = ((unsigned long long)( um ^ 0x80000000u ) << 32 ) | (( e.surfs & 0xFFFF ) ? 1u << 27 : 0u ) | ((uint32_t)s << 11 ) | (uint32_t)k;
+		}
+	}
+	__syncthreads();
+
+	/* B. block bitonic sort of the keys: the order the lines will (nearly) need */
+	if( staged && ne > 1 )
+		for( int32_t k = 2; k <= npow; k <<= 1 )
+			for( int32_t j = k >> 1; j > 0; j >>= 1 )
+			{
+				for( int32_t pr = t; pr < ( npow >> 1 ); pr += EV_THREADS )
+				{
+					const int32_t a = (( pr & ~( j - 1 )) << 1 ) | ( pr & ( j - 1 )), b = a + j;
+					const unsigned long long va = s_key[a], vb = s_key[b];
+					if(( va > vb ) == (( a & k ) == 0 )) { s_key[a] = vb; s_key[b] = va; }
+				}
+				__syncthreads();
+			}
+
+	/* C. band-local surface numbers: rank of the surface among those present in the band, + 1 (order preserving, so
+	 * "lowest set bit = smallest key" still holds in k_lines, with far fewer bit-set words) */
+	int32_t carry = 0;
+	for( int32_t i0 = 0; i0 < bmwords; i0 += EV_THREADS )
+	{
+		const int32_t i = i0 + t;
+		const int32_t v = i < bmwords ? __popc( s_bm[i] ) : 0;
+		const int32_t x = rc_warp_incl_scan( v, lane );
+		if( lane == 31 ) s_warp[warp] = x;
+		__syncthreads();
+		int32_t wbase = 0, tot = 0;
+		for( int k = 0; k < EV_WARPS; k++ )
+		{
+			if( k < warp ) wbase += s_warp[k];
+			tot += s_warp[k];
+		}
+		if( i < bmwords ) s_pre[i] = (uint32_t)( carry + wbase + x - v );
+		carry += tot;
+		__syncthreads();
+	}
+	const int32_t nlocal = carry;
+	uint16_t *bsurf = w.bandsurf + ((size_t)view * nbands + band ) * ( (size_t)w.band_cap + 2 );
+	for( int32_t i = t; i < bmwords; i += EV_THREADS )
+	{
+		uint32_t m = s_bm[i];
+		int32_t r = (int32_t)s_pre[i] + 1;
+		while( m )
+		{
+			bsurf[r++] = (uint16_t)(( i << 5 ) + __ffs( (int)m ) - 1 );
+			m &= m - 1;
+		}
+	}
+	if( t == 0 )
+	{
+		bsurf[0] = 0;
+		w.bandnloc[view * nbands + band] = nlocal;
+	}
+
+	/* 1. events per line: every warp takes a contiguous run of the sorted edge list */
+	const int32_t per = ( ne + EV_WARPS - 1 ) / EV_WARPS;
+	const int32_t k0 = warp * per, k1 = min( ne, k0 + per );
+	int32_t cnt = 0;
+	for( int32_t k = k0; k < k1; k++ )
+	{
+		const uint32_t vv = E[staged ? (int32_t)( (uint32_t)s_key[k] & 2047u ) : k].vv;
 		cnt += ( valid && y >= (int32_t)( vv & 0xFFFF ) && y <= (int32_t)( vv >> 16 )) ? 1 : 0;
 	}
 	s_wcnt[warp][lane] = cnt;
@@ -84,14 +179,18 @@ __global__ void __launch_bounds__( EV_THREADS ) k_events( rc_work_t w )
 	if( !valid || !fits )
 		return;
 
-	/* 2. the events */
+	/* 2. the events, surfaces renumbered band-locally */
 	int32_t pos = off + mybase;
-	for( int32_t k = warp; k < ne; k += EV_WARPS )
+	for( int32_t k = k0; k < k1; k++ )
 	{
-		const rc_edge_t e = gedges[k];
+		const rc_edge_t e = E[staged ? (int32_t)( (uint32_t)s_key[k] & 2047u ) : k];
 		const int32_t v = (int32_t)( e.vv & 0xFFFF );
 		if( y >= v && y <= (int32_t)( e.vv >> 16 ))
-			arena[pos++] = rc_event_key( (int32_t)((uint32_t)e.u + (uint32_t)( y - v ) * (uint32_t)e.u_step ), e.surfs );
+		{
+			const uint32_t tr = e.surfs & 0xFFFF, s = tr ? tr : ( e.surfs >> 16 );
+			const uint32_t loc = s_pre[s >> 5] + (uint32_t)__popc( s_bm[s >> 5] & (( 1u << ( s & 31 )) - 1u )) + 1u;
+			arena[pos++] = rc_event_key( (int32_t)((uint32_t)e.u + (uint32_t)( y - v ) * (uint32_t)e.u_step ), tr ? loc : ( loc << 16 ));
+		}
 	}
 }
 
@@ -126,7 +225,7 @@ __device__ __forceinline__ void rc_sort_smem( unsigned long long *buf, int32_t n
  */
 template <int NW>
 __device__ __forceinline__ int32_t rc_replay_warp( const unsigned long long *keys, int32_t n, int32_t head_iu, int32_t tail_u,
-	rc_span_t *spans, int lane )
+	const uint16_t *bsurf, rc_span_t *spans, int lane )
 {
 	uint32_t st[NW];
 #pragma unroll
@@ -195,7 +294,7 @@ __device__ __forceinline__ int32_t rc_replay_warp( const unsigned long long *key
 		if( emit )
 		{
 			rc_span_t sp;
-			sp.surf = top_before; sp.u = (int16_t)prev; sp.count = (int16_t)( iu - prev );
+			sp.surf = bsurf[top_before]; sp.u = (int16_t)prev; sp.count = (int16_t)( iu - prev );
 			spans[nspans + __popc( em & lt )] = sp;
 		}
 		nspans += __popc( em );
@@ -212,7 +311,7 @@ __device__ __forceinline__ int32_t rc_replay_warp( const unsigned long long *key
 		if( lane == 0 )
 		{
 			rc_span_t sp;
-			sp.surf = top_carry; sp.u = (int16_t)last_u; sp.count = (int16_t)( iu - last_u );
+			sp.surf = bsurf[top_carry]; sp.u = (int16_t)last_u; sp.count = (int16_t)( iu - last_u );
 			spans[nspans] = sp;
 		}
 		nspans++;
@@ -229,7 +328,7 @@ __global__ void __launch_bounds__( LN_WARPS * 32 ) k_lines( rc_work_t w )
 	const int32_t gwarp = blockIdx.x * LN_WARPS + warp, nwarps = gridDim.x * LN_WARPS;
 	const int32_t nlines = w.nviews * w.height;
 	unsigned long long *keys = s_keys[warp];
-	int32_t nspans_total = 0, novf = 0, nserial = 0;
+	int32_t nspans_total = 0, novf = 0, nserial = 0, nsorted = 0;
 #ifdef RC_SPANS_DEBUG
 	const long long dbg_start = clock64();
 #endif
@@ -252,22 +351,38 @@ __global__ void __launch_bounds__( LN_WARPS * 32 ) k_lines( rc_work_t w )
 		if( n <= 32 )
 		{
 			unsigned long long v = lane < n ? slice[lane] : ~0ull;
-			for( int k = 2; k <= 32; k <<= 1 )
-				for( int j = k >> 1; j > 0; j >>= 1 )
-				{
-					const unsigned long long o = __shfl_xor_sync( 0xFFFFFFFFu, v, j );
-					const bool keepmin = (( lane & k ) == 0 ) == (( lane & j ) == 0 );
-					v = keepmin ? ( v < o ? v : o ) : ( v > o ? v : o );
-				}
+			/* k_events wrote the keys in the band's pre-sorted edge order: most lines are in order already */
+			const unsigned long long nx = __shfl_down_sync( 0xFFFFFFFFu, v, 1 );
+			if( __ballot_sync( 0xFFFFFFFFu, lane < 31 && v > nx ))
+			{
+				nsorted++;
+				for( int k = 2; k <= 32; k <<= 1 )
+					for( int j = k >> 1; j > 0; j >>= 1 )
+					{
+						const unsigned long long o = __shfl_xor_sync( 0xFFFFFFFFu, v, j );
+						const bool keepmin = (( lane & k ) == 0 ) == (( lane & j ) == 0 );
+						v = keepmin ? ( v < o ? v : o ) : ( v > o ? v : o );
+					}
+			}
 			keys[lane] = v;
 		}
 		else if( n <= SP_SORTCAP )
 		{
 			int32_t npow = 64;
 			while( npow < n ) npow <<= 1;
-			for( int32_t i = lane; i < npow; i += 32 ) keys[i] = i < n ? slice[i] : ~0ull;
+			bool unsorted = false;
+			for( int32_t i = lane; i < npow; i += 32 )
+			{
+				const unsigned long long v = i < n ? slice[i] : ~0ull;
+				keys[i] = v;
+				unsorted = unsorted || ( i + 1 < n && v > slice[i + 1] );
+			}
 			__syncwarp();
-			rc_sort_smem( keys, npow, lane );
+			if( __ballot_sync( 0xFFFFFFFFu, unsorted ))
+			{
+				nsorted++;
+				rc_sort_smem( keys, npow, lane );
+			}
 		}
 		else
 		{
@@ -287,7 +402,9 @@ __global__ void __launch_bounds__( LN_WARPS * 32 ) k_lines( rc_work_t w )
 		__syncwarp();
 		const long long dbg1 = clock64();
 #endif
-		const int32_t nwords = ( w.ncands[view] + 32 ) >> 5;
+		const int32_t bandix = view * w.nbands + ( line - view * w.height ) / SP_LINES;
+		const uint16_t *bsurf = w.bandsurf + (size_t)bandix * ( (size_t)w.band_cap + 2 );
+		const int32_t nwords = ( w.bandnloc[bandix] + 32 ) >> 5; /* band-local surface numbers */
 		uint32_t *bits = s_bits[warp];
 		if( nwords > SP_BITWORDS )
 			bits = w.scanbits + (size_t)gwarp * (size_t)w.scanbits_words;
@@ -298,10 +415,10 @@ __global__ void __launch_bounds__( LN_WARPS * 32 ) k_lines( rc_work_t w )
 		if( sorted == keys )
 		{
 			/* invalid lanes of a partial round read keys[i >= n]: harmless (never used) */
-			if( nwords <= 2 ) nsp = rc_replay_warp<2>( keys, n, x0, tail_u, reinterpret_cast<rc_span_t *>( slice ), lane );
-			else if( nwords <= 4 ) nsp = rc_replay_warp<4>( keys, n, x0, tail_u, reinterpret_cast<rc_span_t *>( slice ), lane );
-			else if( nwords <= 8 ) nsp = rc_replay_warp<8>( keys, n, x0, tail_u, reinterpret_cast<rc_span_t *>( slice ), lane );
-			else if( nwords <= 16 ) nsp = rc_replay_warp<16>( keys, n, x0, tail_u, reinterpret_cast<rc_span_t *>( slice ), lane );
+			if( nwords <= 2 ) nsp = rc_replay_warp<2>( keys, n, x0, tail_u, bsurf, reinterpret_cast<rc_span_t *>( slice ), lane );
+			else if( nwords <= 4 ) nsp = rc_replay_warp<4>( keys, n, x0, tail_u, bsurf, reinterpret_cast<rc_span_t *>( slice ), lane );
+			else if( nwords <= 8 ) nsp = rc_replay_warp<8>( keys, n, x0, tail_u, bsurf, reinterpret_cast<rc_span_t *>( slice ), lane );
+			else if( nwords <= 16 ) nsp = rc_replay_warp<16>( keys, n, x0, tail_u, bsurf, reinterpret_cast<rc_span_t *>( slice ), lane );
 		}
 		if( nsp < 0 )
 		{
@@ -318,6 +435,9 @@ __global__ void __launch_bounds__( LN_WARPS * 32 ) k_lines( rc_work_t w )
 				nserial++;
 			}
 			nsp = __shfl_sync( 0xFFFFFFFFu, nsp, 0 );
+			__syncwarp();
+			rc_span_t *sp = reinterpret_cast<rc_span_t *>( slice );
+			for( int32_t k = lane; k < nsp; k += 32 ) sp[k].surf = bsurf[sp[k].surf];
 		}
 		if( lane == 0 )
 		{
@@ -344,6 +464,7 @@ __global__ void __launch_bounds__( LN_WARPS * 32 ) k_lines( rc_work_t w )
 		if( nspans_total ) atomicAdd( &w.counters[RC_CTR_SPANS], (unsigned long long)nspans_total );
 		if( novf ) atomicAdd( &w.counters[RC_CTR_OVERFLOW_EVENTS], (unsigned long long)novf );
 		if( nserial ) atomicAdd( &w.counters[RC_CTR_SERIAL_LINES], (unsigned long long)nserial );
+		if( nsorted ) atomicAdd( &w.counters[RC_CTR_SORTED_LINES], (unsigned long long)nsorted );
 	}
 }
 
