@@ -413,9 +413,9 @@ int run_stages( bool timed )
 		const int lblocks = ( nlines + LN_WARPS - 1 ) / LN_WARPS;
 		k_lines<<<lblocks < LN_GRID ? lblocks : LN_GRID, LN_WARPS * 32, 0, st>>>( w ); D.launches++;
 		if( timed ) CK( cudaEventRecord( D.ev[4], st ));
-		const int32_t chunkcap = ( w.width + 7 ) / 8 + SC_SPCAP + 1;
-		dim3 g2(( w.height + DR_WARPS - 1 ) / DR_WARPS, w.nviews );
-		k_draw<<<g2, DR_WARPS * 32, rc_draw_smem( chunkcap ), st>>>( sc, w, chunkcap ); D.launches++;
+		const int32_t chunkcap = rc_draw_chunkcap( w.width );
+		const int dblocks = ( nlines + DR_WARPS - 1 ) / DR_WARPS;
+		k_draw<<<dblocks < DR_GRID ? dblocks : DR_GRID, DR_WARPS * 32, rc_draw_smem( chunkcap ), st>>>( sc, w, chunkcap ); D.launches++;
 	}
 	if( timed ) CK( cudaEventRecord( D.ev[5], st ));
 	CK( cudaGetLastError());
@@ -444,7 +444,7 @@ int rc_dev_init( int device )
 	for( auto &e : D.ev ) CK( cudaEventCreate( &e ));
 	CK( cudaFuncSetAttribute( k_viswalk, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 64 ));
 	CK( cudaFuncSetAttribute( k_events, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_events_smem( 65536 / 32 + 2 )));
-	CK( cudaFuncSetAttribute( k_draw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_draw_smem(( 1920 + 7 ) / 8 + SC_SPCAP + 1 )));
+	CK( cudaFuncSetAttribute( k_draw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_draw_smem( rc_draw_chunkcap( 4096 ))));
 	for( int i = 0; i < 256; i++ ) D.h_styles[i] = 256;
 	if( upload( &D.d_styles, D.h_styles, 256 ) != 0 ) return -1;
 	if( dalloc( &D.d_counters, RC_CTR_COUNT ) != 0 ) return -1;
