@@ -47,7 +47,7 @@ def parse_args():
     ap.add_argument("--views", type=int, default=256, help="views per GPU per step")
     ap.add_argument("--width", type=int, default=320)
     ap.add_argument("--height", type=int, default=240)
-    ap.add_argument("--map", default="small", choices=["tiny", "small", "large"])
+    ap.add_argument("--map", default="small", choices=["tiny", "small", "medium", "large"])
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()

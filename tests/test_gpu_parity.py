@@ -221,3 +221,32 @@ def test_full_c2_batch_properties(cu_small, so_small):
     rc, rz = so.render_views(cams[idx])
     assert (a[idx] == rc).mean() >= TOL and (az[idx] == rz).mean() >= TOL
     assert (a != 0).mean() > 0.95  # the camera list looks at geometry, not at void
+
+
+def test_c3_mechanism_medium_map_1080p(pkg, scene):
+    """C3 at a size the generator finishes quickly: 1920x1080 views of Map M (~12.5k faces, extra light styles),
+    animated style values forcing cache rebuilds.  SURVEY F9: ref_soft silently drops faces past sw_maxsurfs
+    (2000) and edges past sw_maxedges (4000) - both raised in the oracle, before R_NewMap."""
+    m = scene.make_map("medium", ncameras=8)
+    cu = scene.Renderer(pkg.REF_CUDA_PATH, 1920, 1080, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 1920, 1080, m, cvars={"sw_maxsurfs": 60000, "sw_maxedges": 250000})
+    pats = {1: "mmnmmommommnonmmonqnmmo", 2: "abcdefghijklmnopqrstuvwxyzyxwvutsrqponmlkjihgfedcba", 3: "mamamamamama"}
+    for step in range(2):
+        for r in (cu, so):
+            for k, p in pats.items():
+                r.set_lightstyle(k, p, time=step * 0.1 + 0.05)
+            r.set_time(1.0 + step * 0.1)
+            r.run_lightstyles()
+        cc, cz = cu.render_views(m.cameras[:4])
+        rc, rz = so.render_views(m.cameras[:4])
+        assert (cc == rc).mean() >= TOL and (cz == rz).mean() >= TOL, (step, (cc == rc).mean())
+        ctr = cu.counters()
+        assert all(v == 0 for k, v in ctr.items() if k.startswith("overflow")), ctr
+        n = 0
+        for s in range(0, so.host.world_info()["numsurfaces"], 7):
+            for mip in range(4):
+                a, b = so.cache_block(s, mip), cu.cache_block(s, mip)
+                if a is not None and b is not None:
+                    assert np.array_equal(a, b), (step, s, mip)
+                    n += 1
+        assert n > 0

@@ -14,7 +14,7 @@ cu = scene.Renderer(pkg.REF_CUDA_PATH, W, H, m)
 print('device', cu.device_name())
 t = time.time(); cc, cz = cu.render_views(m.cameras[:n]); print('cuda first batch s', time.time() - t)
 print(cu.counters())
-so = scene.Renderer(pkg.REF_SOFT_PATH, W, H, m)
+so = scene.Renderer(pkg.REF_SOFT_PATH, W, H, m, cvars={'sw_maxsurfs': 60000, 'sw_maxedges': 250000})  # ref_soft drops faces past 2000 / edges past 4000 by default
 rc, rz = so.render_views(m.cameras[:n]); print('soft s', so.last_seconds)
 print('colour same', (rc == cc).mean(), 'z same', (rz == cz).mean())
 bad = [(i, float((rc[i] == cc[i]).mean())) for i in range(n) if (rc[i] != cc[i]).any()]

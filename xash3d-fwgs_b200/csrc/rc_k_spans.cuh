@@ -26,6 +26,7 @@
 #define SP_SORTCAP  512  /* events per line the shared-memory sorter takes; longer lines fall back to a serial sort */
 #define SP_BITWORDS 64   /* shared-memory bit-set words per line (views listing <= 2015 faces), else global scratch */
 #define SP_EXCCAP   8
+#define SP_OEPASSES 6  /* odd-even transposition passes tried on a nearly sorted line before the bitonic network */
 
 #if SP_LINES != 32
 #error "k_events maps lanes to scanlines: SP_LINES must be 32"
@@ -353,16 +354,29 @@ __global__ void __launch_bounds__( LN_WARPS * 32 ) k_lines( rc_work_t w )
 			unsigned long long v = lane < n ? slice[lane] : ~0ull;
 			/* k_events wrote the keys in the band's pre-sorted edge order: most lines are in order already */
 			const unsigned long long nx = __shfl_down_sync( 0xFFFFFFFFu, v, 1 );
-			if( __ballot_sync( 0xFFFFFFFFu, lane < 31 && v > nx ))
+			unsigned uns = __ballot_sync( 0xFFFFFFFFu, lane < 31 && v > nx );
+			if( uns )
 			{
+				/* nearly sorted (the band's edge order): a few odd-even transposition passes, else the full network */
 				nsorted++;
-				for( int k = 2; k <= 32; k <<= 1 )
-					for( int j = k >> 1; j > 0; j >>= 1 )
-					{
-						const unsigned long long o = __shfl_xor_sync( 0xFFFFFFFFu, v, j );
-						const bool keepmin = (( lane & k ) == 0 ) == (( lane & j ) == 0 );
-						v = keepmin ? ( v < o ? v : o ) : ( v > o ? v : o );
-					}
+				for( int pass = 0; uns && pass < SP_OEPASSES; pass++ )
+				{
+					unsigned long long o = __shfl_xor_sync( 0xFFFFFFFFu, v, 1 );
+					v = ( lane & 1 ) ? ( v > o ? v : o ) : ( v < o ? v : o );
+					const unsigned long long up = __shfl_down_sync( 0xFFFFFFFFu, v, 1 ), dn = __shfl_up_sync( 0xFFFFFFFFu, v, 1 );
+					if( lane & 1 ) { if( lane < 31 && up < v ) v = up; }
+					else if( lane > 0 && dn > v ) v = dn;
+					const unsigned long long nx2 = __shfl_down_sync( 0xFFFFFFFFu, v, 1 );
+					uns = __ballot_sync( 0xFFFFFFFFu, lane < 31 && v > nx2 );
+				}
+				if( uns )
+					for( int k = 2; k <= 32; k <<= 1 )
+						for( int j = k >> 1; j > 0; j >>= 1 )
+						{
+							const unsigned long long o = __shfl_xor_sync( 0xFFFFFFFFu, v, j );
+							const bool keepmin = (( lane & k ) == 0 ) == (( lane & j ) == 0 );
+							v = keepmin ? ( v < o ? v : o ) : ( v > o ? v : o );
+						}
 			}
 			keys[lane] = v;
 		}
@@ -378,10 +392,26 @@ __global__ void __launch_bounds__( LN_WARPS * 32 ) k_lines( rc_work_t w )
 				unsorted = unsorted || ( i + 1 < n && v > slice[i + 1] );
 			}
 			__syncwarp();
-			if( __ballot_sync( 0xFFFFFFFFu, unsorted ))
+			unsigned uns = __ballot_sync( 0xFFFFFFFFu, unsorted );
+			if( uns )
 			{
 				nsorted++;
-				rc_sort_smem( keys, npow, lane );
+				for( int pass = 0; uns && pass < SP_OEPASSES; pass++ )
+				{
+					bool sw = false;
+					for( int ph = 0; ph < 2; ph++ )
+					{
+						for( int32_t a = 2 * lane + ph; a + 1 < n; a += 64 )
+						{
+							const unsigned long long va = keys[a], vb = keys[a + 1];
+							if( va > vb ) { keys[a] = vb; keys[a + 1] = va; sw = true; }
+						}
+						__syncwarp();
+					}
+					uns = __ballot_sync( 0xFFFFFFFFu, sw );
+				}
+				if( uns )
+					rc_sort_smem( keys, npow, lane );
 			}
 		}
 		else

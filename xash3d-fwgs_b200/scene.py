@@ -41,7 +41,7 @@ CTR_NAMES = ["views", "pixels", "cands", "surfs", "edges", "spans", "cache_block
 @functools.lru_cache(maxsize=8)
 def make_map(which: str = "small", ncameras: int = 256, **kw):
     """Named synthetic worlds of BASELINE.json: tiny (unit tests), small (Map S: C1/C2/C5), large (Map L: C3)."""
-    spec = {"tiny": mapgen.spec_tiny, "small": mapgen.spec_small, "large": mapgen.spec_large}[which](**kw)
+    spec = {"tiny": mapgen.spec_tiny, "small": mapgen.spec_small, "medium": mapgen.spec_medium, "large": mapgen.spec_large}[which](**kw)
     return mapgen.generate(spec, ncameras=ncameras)
 
 

@@ -732,6 +732,13 @@ def spec_tiny(seed=0xB200, **kw) -> MapSpec:
     return MapSpec(rooms=(2, 2, 1), seed=seed, name="synth_t", **kw)
 
 
+def spec_medium(seed=0xB203, **kw) -> MapSpec:
+    """Map M: 12x12x3 rooms, ~12.5k faces, extra light styles on 25% of faces: the C3 mechanism (1080p, animated
+    light styles, cache rebuilds) at a size the generator finishes in ~20 s (Map L takes many minutes to generate)."""
+    kw.setdefault("extra_styles_prob", (1, 4))
+    return MapSpec(rooms=(12, 12, 3), seed=seed, name="synth_m", **kw)
+
+
 def spec_large(seed=0xB203, **kw) -> MapSpec:
     """Map L: 24x24x4 rooms, ~30k faces, extra light styles on 25% of faces (C3)."""
     return MapSpec(rooms=(24, 24, 4), seed=seed, name="synth_l", extra_styles_prob=(1, 4), **kw)
