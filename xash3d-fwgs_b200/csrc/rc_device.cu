@@ -393,7 +393,11 @@ int run_stages( bool timed )
 	CK( cudaMemsetAsync( D.d_nlist, 0, sizeof( int32_t ) * 2, st ));
 	CK( cudaMemsetAsync( w.bandcnt, 0, sizeof( int32_t ) * (size_t)w.nviews * w.nbands, st ));
 	if( timed ) CK( cudaEventRecord( D.ev[0], st ));
-	k_viswalk<<<w.nviews, VW_THREADS, (size_t)w.vis_smem, st>>>( sc, w ); D.launches++;
+	if( w.vis_stage & VW_STAGE_TREE )
+		k_viswalk<VW_THREADS_SMALL><<<w.nviews, VW_THREADS_SMALL, (size_t)w.vis_smem, st>>>( sc, w );
+	else
+		k_viswalk<VW_THREADS_BIG><<<w.nviews, VW_THREADS_BIG, (size_t)w.vis_smem, st>>>( sc, w );
+	D.launches++;
 	if( timed ) CK( cudaEventRecord( D.ev[1], st ));
 	{
 		dim3 g(( w.max_cands + 127 ) / 128, w.nviews );
@@ -442,7 +446,8 @@ int rc_dev_init( int device )
 	D.device = device;
 	CK( cudaStreamCreateWithFlags( &D.stream, cudaStreamNonBlocking ));
 	for( auto &e : D.ev ) CK( cudaEventCreate( &e ));
-	CK( cudaFuncSetAttribute( k_viswalk, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 64 ));
+	CK( cudaFuncSetAttribute( k_viswalk<VW_THREADS_SMALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 64 ));
+	CK( cudaFuncSetAttribute( k_viswalk<VW_THREADS_BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 64 ));
 	CK( cudaFuncSetAttribute( k_events, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_events_smem( 65536 / 32 + 2 )));
 	CK( cudaFuncSetAttribute( k_draw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_draw_smem( rc_draw_chunkcap( 4096 ))));
 	for( int i = 0; i < 256; i++ ) D.h_styles[i] = 256;

@@ -24,7 +24,8 @@
 #ifndef RC_K_VIS_CUH
 #define RC_K_VIS_CUH
 
-#define VW_THREADS 128
+#define VW_THREADS_SMALL 128 /* tree staged in shared memory: many views, short chains */
+#define VW_THREADS_BIG   512 /* big trees walked in HBM: few views, hide the latency with threads */
 #define VW_MAXLVL  1024
 #define VW_PVSCAP  32   /* leaves inside the fat-PVS radius handled by the parallel OR (r_pvs_radius is 0.1) */
 
@@ -45,13 +46,45 @@ static inline size_t rc_vis_tree_bytes( const rc_scene_t *sc )
 	return sizeof( rc_node_t ) * (size_t)sc->numnodes + sizeof( rc_plane_t ) * (size_t)sc->numplanes + sizeof( rc_leaf_t ) * (size_t)sc->numleafs;
 }
 
+template <int VW_THREADS>
 __device__ __forceinline__ void rc_stage_copy( void *dst, const void *src, size_t bytes, int t )
 {
 	uint4 *d = reinterpret_cast<uint4 *>( dst );
 	const uint4 *s = reinterpret_cast<const uint4 *>( src );
-	for( size_t i = t; i < bytes / 16; i += VW_THREADS ) d[i] = s[i];
+	const size_t n = bytes / 16;
+	size_t i = t;
+	for( ; i + 3 * VW_THREADS < n; i += 4 * VW_THREADS )
+	{
+		/* four loads in flight per thread */
+		const uint4 a = s[i], b = s[i + VW_THREADS], c = s[i + 2 * VW_THREADS], e = s[i + 3 * VW_THREADS];
+		d[i] = a; d[i + VW_THREADS] = b; d[i + 2 * VW_THREADS] = c; d[i + 3 * VW_THREADS] = e;
+	}
+	for( ; i < n; i += VW_THREADS ) d[i] = s[i];
 }
 
+/* rc_cull_box with float compares: ( (double)dot - (double)dist ) has the sign of ( dot - dist ), so "d <= 0" is
+ * "dot <= dist" and "d >= 0" is "dot >= dist" (r_bsp.c:483-520) */
+__device__ __forceinline__ int32_t rc_cull_box_f( const rc_view_t *vw, const float *minmaxs, int32_t clipflags )
+{
+#pragma unroll
+	for( int i = 0; i < 4; i++ )
+	{
+		if( !( clipflags & ( 1 << i )))
+			continue;
+		const int32_t *pindex = vw->frustum_idx[i];
+		const float *nrm = vw->clip_normal[i];
+		const float dist = vw->clip_dist[i];
+		const float rj = minmaxs[pindex[0]] * nrm[0] + minmaxs[pindex[1]] * nrm[1] + minmaxs[pindex[2]] * nrm[2];
+		if( rj <= dist )
+			return -1;
+		const float ac = minmaxs[pindex[3]] * nrm[0] + minmaxs[pindex[4]] * nrm[1] + minmaxs[pindex[5]] * nrm[2];
+		if( ac >= dist )
+			clipflags &= ~( 1 << i );
+	}
+	return clipflags;
+}
+
+template <int VW_THREADS>
 __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_work_t w )
 {
 	extern __shared__ __align__( 16 ) uint32_t s_bits[];
@@ -59,6 +92,7 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 	__shared__ int32_t s_n, s_nleaf, s_npvs, s_allvis, s_ovf;
 	__shared__ int32_t s_pvsleaf[VW_PVSCAP];
 	__shared__ int32_t s_warp[VW_THREADS / 32];
+	__shared__ rc_view_t s_view;
 
 	const int view = blockIdx.x, t = threadIdx.x, lane = t & 31, warp = t >> 5;
 #ifdef RC_SPANS_DEBUG
@@ -68,7 +102,9 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 #define VW_MARK() do { } while( 0 )
 #endif
 	VW_MARK();
-	const rc_view_t *vw = &w.views[view];
+	if( t < (int)( sizeof( rc_view_t ) / 4 ))
+		reinterpret_cast<uint32_t *>( &s_view )[t] = reinterpret_cast<const uint32_t *>( &w.views[view] )[t];
+	const rc_view_t *vw = &s_view;
 	const int32_t viswords = w.visbytes_padded >> 2;
 	uint32_t *vis = s_bits;
 	uint32_t *nodevis = vis + viswords;
@@ -82,11 +118,11 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 		unsigned char *p = reinterpret_cast<unsigned char *>( s_bits ) + (((size_t)allwords * 4 + 15 ) & ~(size_t)15 );
 		if( w.vis_stage & VW_STAGE_TREE )
 		{
-			rc_stage_copy( p, sc.nodes, sizeof( rc_node_t ) * (size_t)sc.numnodes, t );
+			rc_stage_copy<VW_THREADS>( p, sc.nodes, sizeof( rc_node_t ) * (size_t)sc.numnodes, t );
 			sc.nodes = reinterpret_cast<const rc_node_t *>( p ); p += sizeof( rc_node_t ) * (size_t)sc.numnodes;
-			rc_stage_copy( p, sc.planes, sizeof( rc_plane_t ) * (size_t)sc.numplanes, t );
+			rc_stage_copy<VW_THREADS>( p, sc.planes, sizeof( rc_plane_t ) * (size_t)sc.numplanes, t );
 			sc.planes = reinterpret_cast<const rc_plane_t *>( p ); p += sizeof( rc_plane_t ) * (size_t)sc.numplanes;
-			rc_stage_copy( p, sc.leafs, sizeof( rc_leaf_t ) * (size_t)sc.numleafs, t );
+			rc_stage_copy<VW_THREADS>( p, sc.leafs, sizeof( rc_leaf_t ) * (size_t)sc.numleafs, t );
 			sc.leafs = reinterpret_cast<const rc_leaf_t *>( p ); p += sizeof( rc_leaf_t ) * (size_t)sc.numleafs;
 		}
 		if( w.vis_stage & VW_STAGE_SCRATCH )
@@ -111,13 +147,15 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 			s_allvis = 1;
 		else
 		{
-			const int32_t viewleaf = rc_point_in_leaf( &sc, vw->origin );
-			if( !sc.visdata_len || sc.leafs[viewleaf].cluster < 0 )
+			/* one walk for Mod_PointInLeaf and Mod_FatPVS: where both sides are within the radius the walk follows
+			 * the side the eye is on (d <= 0: back) and defers the other, so the first leaf reached is the view leaf */
+			if( !sc.visdata_len )
 				s_allvis = 1;
 			else
 			{
 				int32_t *stack = seq; /* free until P5 */
 				int32_t sp = 0, node = sc.headnode, np = 0;
+				bool first = true;
 				for( ;; )
 				{
 					while( node >= 0 )
@@ -128,11 +166,18 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 						else if( d < -vw->pvs_radius ) node = nd->child[1];
 						else
 						{
-							if( sp < cap ) stack[sp++] = nd->child[1];
-							node = nd->child[0];
+							const int near = d <= 0 ? 1 : 0;
+							if( sp < cap ) stack[sp++] = nd->child[!near];
+							node = nd->child[near];
 						}
 					}
 					const int32_t li = -1 - node;
+					if( first && sc.leafs[li].cluster < 0 )
+					{
+						s_allvis = 1;
+						break;
+					}
+					first = false;
 					if( sc.leafs[li].cluster >= 0 )
 					{
 						if( np < VW_PVSCAP ) s_pvsleaf[np++] = li;
@@ -213,7 +258,7 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 				const int32_t li = -1 - ref;
 				const rc_leaf_t *leaf = &sc.leafs[li];
 				if( leaf->contents != RC_CONTENTS_SOLID && rc_testbit( leafmark, li )
-					&& !( clipflags && rc_cull_box( vw, leaf->minmaxs, clipflags ) < 0 ))
+					&& !( clipflags && rc_cull_box_f( vw, leaf->minmaxs, clipflags ) < 0 ))
 				{
 					alive = 1;
 					leaflist[atomicAdd( &s_nleaf, 1 )] = e;
@@ -223,7 +268,7 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 			{
 				const rc_node_t *node = &sc.nodes[ref];
 				if( clipflags )
-					clipflags = rc_cull_box( vw, node->minmaxs, clipflags );
+					clipflags = rc_cull_box_f( vw, node->minmaxs, clipflags );
 				if( clipflags >= 0 )
 				{
 					alive = 1;
