@@ -330,7 +330,7 @@ int ensure_batch( int nviews, int width, int height )
 	w.nodewords = ( sc.numnodes + 31 ) / 32 + 1;
 	w.leafwords = ( sc.numleafs + 31 ) / 32 + 1;
 	w.surfwords = ( sc.numsurfaces + 31 ) / 32 + 1;
-	w.stack_ints = (int32_t)rc_vis_scratch_ints( sc.numnodes );
+	w.stack_ints = (int32_t)rc_vis_scratch_ints2( sc.numnodes, sc.numleafs );
 	{
 		const size_t budget = 200 * 1024;
 		size_t need = ((((size_t)( w.visbytes_padded >> 2 ) + w.nodewords + w.leafwords + w.surfwords ) * 4 ) + 15 ) & ~(size_t)15;
@@ -341,6 +341,11 @@ int ensure_batch( int nviews, int width, int height )
 			if( need + (size_t)w.stack_ints * 4 <= budget )
 			{
 				w.vis_stage |= VW_STAGE_SCRATCH; need += (size_t)w.stack_ints * 4;
+				const size_t lists = (( 2 * ( (size_t)sc.numsurfaces + sc.nummarks )) + 15 ) & ~(size_t)15;
+				if( need + lists <= budget )
+				{
+					w.vis_stage |= VW_STAGE_LISTS; need += lists;
+				}
 			}
 		}
 		w.vis_smem = (int32_t)need;

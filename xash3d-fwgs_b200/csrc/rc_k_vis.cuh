@@ -36,10 +36,17 @@ static inline size_t rc_vis_scratch_ints( int32_t numnodes )
 	return 8 * cap + (size_t)numnodes + 8;
 }
 
+/* + per-node / per-leaf frustum flags of the view (phase A) */
+static inline size_t rc_vis_scratch_ints2( int32_t numnodes, int32_t numleafs )
+{
+	return rc_vis_scratch_ints( numnodes ) + (size_t)numnodes + (size_t)numleafs;
+}
+
 /* dynamic shared memory: bit sets, then (when they fit, w.vis_stage) a private copy of the BSP tree records and the
  * per-view scratch - the walk is a chain of dependent loads, shared memory cuts every link from ~300 to ~30 cycles */
 #define VW_STAGE_TREE    1
 #define VW_STAGE_SCRATCH 2
+#define VW_STAGE_LISTS   4 /* surfnode + marksurfaces as u16 */
 
 static inline size_t rc_vis_tree_bytes( const rc_scene_t *sc )
 {
@@ -52,14 +59,42 @@ __device__ __forceinline__ void rc_stage_copy( void *dst, const void *src, size_
 	uint4 *d = reinterpret_cast<uint4 *>( dst );
 	const uint4 *s = reinterpret_cast<const uint4 *>( src );
 	const size_t n = bytes / 16;
+	if( !n ) return;
+	/* every block copies the same bytes at the same time: start each one at a different place so that the
+	 * requests spread over the L2 slices instead of queueing on one */
+	const size_t rot = ((size_t)blockIdx.x * 37 ) % n;
 	size_t i = t;
 	for( ; i + 3 * VW_THREADS < n; i += 4 * VW_THREADS )
 	{
-		/* four loads in flight per thread */
-		const uint4 a = s[i], b = s[i + VW_THREADS], c = s[i + 2 * VW_THREADS], e = s[i + 3 * VW_THREADS];
-		d[i] = a; d[i + VW_THREADS] = b; d[i + 2 * VW_THREADS] = c; d[i + 3 * VW_THREADS] = e;
+		size_t i0 = i + rot, i1 = i0 + VW_THREADS, i2 = i1 + VW_THREADS, i3 = i2 + VW_THREADS;
+		if( i0 >= n ) i0 -= n; if( i1 >= n ) i1 -= n; if( i2 >= n ) i2 -= n; if( i3 >= n ) i3 -= n;
+		const uint4 a = s[i0], b = s[i1], c = s[i2], e = s[i3]; /* four loads in flight per thread */
+		d[i0] = a; d[i1] = b; d[i2] = c; d[i3] = e;
 	}
-	for( ; i < n; i += VW_THREADS ) d[i] = s[i];
+	for( ; i < n; i += VW_THREADS )
+	{
+		size_t i0 = i + rot;
+		if( i0 >= n ) i0 -= n;
+		d[i0] = s[i0];
+	}
+}
+
+/* frustum tests of one bbox against all four planes, no early out: bits 0..3 = trivially accepted, 4..7 = rejected */
+__device__ __forceinline__ int32_t rc_box_flags( const rc_view_t *vw, const float *minmaxs )
+{
+	int32_t f = 0;
+#pragma unroll
+	for( int i = 0; i < 4; i++ )
+	{
+		const int32_t *pindex = vw->frustum_idx[i];
+		const float *nrm = vw->clip_normal[i];
+		const float dist = vw->clip_dist[i];
+		const float rj = minmaxs[pindex[0]] * nrm[0] + minmaxs[pindex[1]] * nrm[1] + minmaxs[pindex[2]] * nrm[2];
+		const float ac = minmaxs[pindex[3]] * nrm[0] + minmaxs[pindex[4]] * nrm[1] + minmaxs[pindex[5]] * nrm[2];
+		if( rj <= dist ) f |= 16 << i;
+		if( ac >= dist ) f |= 1 << i;
+	}
+	return f;
 }
 
 /* rc_cull_box with float compares: ( (double)dot - (double)dist ) has the sign of ( dot - dist ), so "d <= 0" is
@@ -114,6 +149,7 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 
 	const int32_t cap = 2 * sc.numnodes + 2;
 	int32_t *scr = w.walkstack + (size_t)view * w.stack_ints;
+	const uint16_t *sn16 = nullptr, *mk16 = nullptr;
 	{
 		unsigned char *p = reinterpret_cast<unsigned char *>( s_bits ) + (((size_t)allwords * 4 + 15 ) & ~(size_t)15 );
 		if( w.vis_stage & VW_STAGE_TREE )
@@ -126,12 +162,23 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 			sc.leafs = reinterpret_cast<const rc_leaf_t *>( p ); p += sizeof( rc_leaf_t ) * (size_t)sc.numleafs;
 		}
 		if( w.vis_stage & VW_STAGE_SCRATCH )
-			scr = reinterpret_cast<int32_t *>( p );
+		{
+			scr = reinterpret_cast<int32_t *>( p ); p += sizeof( int32_t ) * (size_t)w.stack_ints;
+		}
+		if( w.vis_stage & VW_STAGE_LISTS )
+		{
+			/* BSP30 caps nodes and faces at 65535: 16 bits are enough */
+			uint16_t *a = reinterpret_cast<uint16_t *>( p ), *b = a + sc.numsurfaces;
+			for( int i = t; i < sc.numsurfaces; i += VW_THREADS ) a[i] = (uint16_t)sc.surfnode[i];
+			for( int i = t; i < sc.nummarks; i += VW_THREADS ) b[i] = (uint16_t)sc.marksurfaces[i];
+			sn16 = a; mk16 = b;
+		}
 	}
 	int32_t *e_ref = scr, *e_info = scr + cap, *e_child = scr + 2 * (size_t)cap, *e_size = scr + 3 * (size_t)cap;
 	int32_t *e_pos = scr + 4 * (size_t)cap, *seq = scr + 5 * (size_t)cap, *leaflist = scr + 6 * (size_t)cap;
 	int32_t *posclip = scr + 7 * (size_t)cap;
 	int32_t *nodepos = scr + 8 * (size_t)cap;
+	int32_t *nflag = nodepos + sc.numnodes + 8, *lflag = nflag + sc.numnodes;
 
 	for( int i = t; i < allwords; i += VW_THREADS ) s_bits[i] = 0;
 	for( int i = t; i < sc.numnodes; i += VW_THREADS ) nodepos[i] = -1; /* not visited: precedes no leaf */
@@ -232,6 +279,26 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 	}
 	__syncthreads();
 
+	/* phase A: everything about a visible node / leaf that depends on the view only - frustum flags of its bbox,
+	 * the side of its plane the eye is on, which of its faces look at the eye - for all of them at once, so that the
+	 * level-by-level descent below is bit logic */
+	for( int i = t; i < sc.numnodes; i += VW_THREADS )
+	{
+		if( !rc_testbit( nodevis, i ))
+			continue;
+		const rc_node_t *node = &sc.nodes[i];
+		const double dot = rc_node_dot( vw, &sc.planes[node->plane] );
+		const int32_t want = dot < -RC_BACKFACE_EPSILON ? 1 : ( dot > RC_BACKFACE_EPSILON ? 0 : 2 );
+		nflag[i] = rc_box_flags( vw, node->minmaxs ) | (( dot >= 0 ? 0 : 1 ) << 8 ) | ( want << 9 );
+	}
+	for( int i = t; i < sc.numleafs; i += VW_THREADS )
+	{
+		if( !rc_testbit( leafmark, i ))
+			continue;
+		const rc_leaf_t *leaf = &sc.leafs[i];
+		lflag[i] = leaf->contents == RC_CONTENTS_SOLID ? 0xF0 | 256 : rc_box_flags( vw, leaf->minmaxs );
+	}
+	__syncthreads();
 	VW_MARK(); /* 3: mark leaves */
 	/* P1: level-synchronous descent */
 	int32_t nlvl = 0;
@@ -256,23 +323,28 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 			if( ref < 0 )
 			{
 				const int32_t li = -1 - ref;
-				const rc_leaf_t *leaf = &sc.leafs[li];
-				if( leaf->contents != RC_CONTENTS_SOLID && rc_testbit( leafmark, li )
-					&& !( clipflags && rc_cull_box_f( vw, leaf->minmaxs, clipflags ) < 0 ))
+				if( rc_testbit( leafmark, li ))
 				{
-					alive = 1;
-					leaflist[atomicAdd( &s_nleaf, 1 )] = e;
+					const int32_t f = lflag[li];
+					if( !( f & 256 ) && !(( f >> 4 ) & clipflags ))
+					{
+						alive = 1;
+						leaflist[atomicAdd( &s_nleaf, 1 )] = e;
+					}
 				}
 			}
 			else if( rc_testbit( nodevis, ref ))
 			{
-				const rc_node_t *node = &sc.nodes[ref];
-				if( clipflags )
-					clipflags = rc_cull_box_f( vw, node->minmaxs, clipflags );
-				if( clipflags >= 0 )
+				/* R_RecursiveWorldNode tests the planes in order and stops at the first rejection; a plane is only
+				 * tested while its flag is still set, and flags only ever get cleared: the outcome is the same as
+				 * "any still-flagged plane rejects" */
+				const int32_t f = nflag[ref];
+				if( !(( f >> 4 ) & clipflags ))
 				{
 					alive = 1;
-					const int side = rc_node_dot( vw, &sc.planes[node->plane] ) >= 0 ? 0 : 1;
+					clipflags &= ~f & 15;
+					const int side = ( f >> 8 ) & 1;
+					const rc_node_t *node = &sc.nodes[ref];
 					child = atomicAdd( &s_n, 2 );
 					e_ref[child] = node->child[side]; e_info[child] = clipflags;
 					e_ref[child + 1] = node->child[!side]; e_info[child + 1] = clipflags;
@@ -341,8 +413,8 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 			const int32_t m0 = leaf->firstmark, m1 = m0 + leaf->nummark;
 			for( int32_t m = m0 + lane; m < m1; m += 32 )
 			{
-				const int32_t s = sc.marksurfaces[m];
-				if( pos < nodepos[sc.surfnode[s]] )
+				const int32_t s = mk16 ? (int32_t)mk16[m] : sc.marksurfaces[m];
+				if( pos < nodepos[sn16 ? (int32_t)sn16[s] : sc.surfnode[s]] )
 					atomicOr( &surfmark[s >> 5], 1u << ( s & 31 ));
 			}
 		}
@@ -363,9 +435,8 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 		{
 			const int32_t s = ( wi << 5 ) + __ffs( (int)m ) - 1;
 			m &= m - 1;
-			const int32_t n = sc.surfnode[s];
-			const double dot = rc_node_dot( vw, &sc.planes[sc.nodes[n].plane] );
-			const int want = dot < -RC_BACKFACE_EPSILON ? 1 : ( dot > RC_BACKFACE_EPSILON ? 0 : -1 );
+			const int32_t n = sn16 ? (int32_t)sn16[s] : sc.surfnode[s];
+			const int want = ( nflag[n] >> 9 ) & 3; /* 2: the eye is on the plane, nothing is posted */
 			const int back = ( sc.surfback[wi] >> ( s & 31 )) & 1;
 			if( back == want )
 				atomicAdd( &seq[nodepos[n]], 1 );
@@ -401,7 +472,7 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 		{
 			const int32_t b = __ffs( (int)m ) - 1, s = ( wi << 5 ) + b;
 			m &= m - 1;
-			const int32_t n = sc.surfnode[s], pos = nodepos[n];
+			const int32_t n = sn16 ? (int32_t)sn16[s] : sc.surfnode[s], pos = nodepos[n];
 			/* rank among the node's candidates: surviving marks in [firstsurface, s) */
 			const int32_t f = sc.nodes[n].firstsurface;
 			int32_t rank = 0;
