@@ -185,9 +185,60 @@ __global__ void __launch_bounds__( 256 ) k_cache_list( rc_scene_t sc, rc_work_t 
 		w.cache_list[atomicAdd( w.cache_nlist, 1 )] = slot;
 }
 
+/*
+ * R_DrawSurface + R_DrawSurfaceBlock8_mipN (r_surf.c:291-757) for runs of RL texels of one row inside one light
+ * block: the light ramp of the row is set up once per run (uint32 wraparound arithmetic as in the reference), the RL
+ * texels leave as one 4/8/16-byte store.  s_rc[bv * nbu + bu] = source offset of the block's first texel (the
+ * reference's psource after its column / row wrap rules, rc_cache_texel).
+ */
+template <int RL>
+__device__ __forceinline__ void rc_cache_runs( const rc_scene_t &sc, const rc_texture_t *tex, int32_t mip, const uint32_t *s_bl, int32_t lightwidth,
+	const int32_t *s_rc, int32_t nbu, uint16_t *dst, int32_t bw, int32_t bh, int tid )
+{
+	const int32_t k = 4 - mip, bs = 16 >> mip;
+	int32_t smaxt = tex->width >> mip;
+	if( smaxt < 1 ) smaxt = 1;
+	const int32_t lim = tex->width * tex->height * 2;
+	const uint16_t *__restrict__ src = sc.texels + tex->ofs[mip];
+	const uint16_t *__restrict__ cmap = sc.colormap;
+	const int32_t rpr = bw / RL, total = rpr * bh;
+
+	for( int32_t r = tid; r < total; r += CACHE_THREADS )
+	{
+		const int32_t y = r / rpr, x = ( r - y * rpr ) * RL;
+		const int32_t bu = x >> k, b0 = x & ( bs - 1 ), bv = y >> k, i = y & ( bs - 1 );
+		const uint32_t *lp = s_bl + bv * lightwidth + bu;
+		uint32_t ll = lp[0], lr = lp[1];
+		const uint32_t lls = ( lp[lightwidth] - ll ) >> k, lrs = ( lp[lightwidth + 1] - lr ) >> k;
+		ll += (uint32_t)i * lls; lr += (uint32_t)i * lrs;
+		const uint32_t step = ( ll - lr ) >> k;
+		uint32_t light = lr + (uint32_t)( bs - 1 - b0 ) * step;
+		const int32_t idx0 = s_rc[bv * nbu + bu] + i * smaxt + b0;
+		uint32_t packed[RL / 2];
+#pragma unroll
+		for( int j = 0; j < RL; j++ )
+		{
+			/* the reference reads past the mip when a texture is not a multiple of the block size; stay inside the arena */
+			int32_t idx = idx0 + j;
+			idx = idx < 0 ? 0 : ( idx >= lim ? lim - 1 : idx );
+			const uint32_t pix = __ldg( src + idx );
+			uint32_t o = (uint32_t)__ldg( cmap + (( pix >> 3 ) | (( light & 0x1f00u ) << 5 ))) | ( pix & 7u );
+			if( mip == 0 && pix == RC_TRANSPARENT_COLOR )
+				o = RC_TRANSPARENT_COLOR;
+			if( j & 1 ) packed[j >> 1] |= o << 16; else packed[j >> 1] = o;
+			light -= step;
+		}
+		uint16_t *out = dst + (size_t)y * bw + x;
+		if( RL == 8 ) *reinterpret_cast<uint4 *>( out ) = make_uint4( packed[0], packed[1], packed[2 % ( RL / 2 )], packed[3 % ( RL / 2 )] );
+		else if( RL == 4 ) *reinterpret_cast<uint2 *>( out ) = make_uint2( packed[0], packed[1 % ( RL / 2 )] );
+		else *reinterpret_cast<uint32_t *>( out ) = packed[0];
+	}
+}
+
 __global__ void __launch_bounds__( CACHE_THREADS ) k_cache_build( rc_scene_t sc, rc_work_t w )
 {
 	__shared__ uint32_t s_bl[CACHE_LUXCAP];
+	__shared__ int32_t s_rc[CACHE_LUXCAP];
 	__shared__ int32_t s_item;
 	const int tid = threadIdx.x;
 	const int32_t nlist = *w.cache_nlist;
@@ -213,22 +264,58 @@ __global__ void __launch_bounds__( CACHE_THREADS ) k_cache_build( rc_scene_t sc,
 		}
 		for( int32_t i = tid; i < size; i += CACHE_THREADS )
 			s_bl[i] = rc_blocklight( &sc, sf, w.styles, size, i );
-		__syncthreads();
 
 		const int32_t bw = sf->lightextents[0] >> mip, bh = sf->lightextents[1] >> mip;
+		const int32_t k = 4 - mip, bs = 16 >> mip;
+		const int32_t nbu = bw >> k, nbv = bh >> k;
 		uint16_t *dst = sc.cache + sf->cache_ofs[mip];
-		for( int32_t i = tid; i < bw * bh; i += CACHE_THREADS )
+		const bool fast = nbu * bs == bw && nbv * bs == bh && nbu < smax && nbv < tmax && nbu * nbv <= CACHE_LUXCAP;
+		if( fast )
 		{
-			int32_t y = i / bw, x = i - y * bw;
-			dst[i] = rc_cache_texel( &sc, sf, tex, mip, s_bl, smax, x, y );
+			/* source offset of every light block: column offset advances per block column and snaps to 0 past the
+			 * texture width, row offset advances per block row and steps back by the texture size (r_surf.c:411-426,586-600) */
+			int32_t smaxt = tex->width >> mip, tmaxt = tex->height >> mip;
+			if( smaxt < 1 ) smaxt = 1;
+			if( tmaxt < 1 ) tmaxt = 1;
+			const int32_t total = tmaxt * smaxt;
+			for( int32_t bu = tid; bu < nbu; bu += CACHE_THREADS )
+			{
+				int32_t soffset = ((( (int32_t)sf->lightmapmins[0] ) >> mip ) + ( smaxt << 16 )) % smaxt;
+				for( int32_t q = 0; q < bu; q++ )
+				{
+					soffset += bs;
+					if( soffset >= smaxt ) soffset = 0;
+				}
+				int32_t rowofs = (((( (int32_t)sf->lightmapmins[1] ) >> mip ) + ( tmaxt << 16 )) % tmaxt ) * smaxt;
+				for( int32_t bv = 0; bv < nbv; bv++ )
+				{
+					s_rc[bv * nbu + bu] = rowofs + soffset;
+					rowofs += bs * smaxt;
+					if( rowofs + soffset >= total ) rowofs -= total;
+				}
+			}
 		}
+		__syncthreads();
+
+		if( !fast )
+		{
+			for( int32_t i = tid; i < bw * bh; i += CACHE_THREADS )
+			{
+				int32_t y = i / bw, x = i - y * bw;
+				dst[i] = rc_cache_texel( &sc, sf, tex, mip, s_bl, smax, x, y );
+			}
+		}
+		else if( mip <= 1 ) rc_cache_runs<8>( sc, tex, mip, s_bl, smax, s_rc, nbu, dst, bw, bh, tid );
+		else if( mip == 2 ) rc_cache_runs<4>( sc, tex, mip, s_bl, smax, s_rc, nbu, dst, bw, bh, tid );
+		else rc_cache_runs<2>( sc, tex, mip, s_bl, smax, s_rc, nbu, dst, bw, bh, tid );
+
 		if( tid == 0 )
 		{
-			rc_cachekey_t *k = &w.cache_keys[slot];
-			k->texnum = sf->texnum;
+			rc_cachekey_t *kk = &w.cache_keys[slot];
+			kk->texnum = sf->texnum;
 			for( int j = 0; j < RC_MAXLIGHTMAPS; j++ )
-				k->light[j] = sf->styles[j] != 255 ? w.styles[sf->styles[j]] : 0;
-			k->valid = 1;
+				kk->light[j] = sf->styles[j] != 255 ? w.styles[sf->styles[j]] : 0;
+			kk->valid = 1;
 			atomicAdd( &w.counters[RC_CTR_CACHE_BLOCKS], 1ull );
 			atomicAdd( &w.counters[RC_CTR_CACHE_TEXELS], (unsigned long long)bw * bh );
 		}
