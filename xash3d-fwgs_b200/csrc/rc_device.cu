@@ -71,6 +71,7 @@ struct rc_work_t
 
 #define SP_LINES 32 /* scanlines per band (rc_k_spans.cuh): k_faces bins edges by band */
 #define LN_GRID  ( 148 * 12 ) /* k_lines blocks: 12 resident blocks of 4 warps per SM */
+#define RC_COPY_SLICES 8 /* rc_dev_render: view slices drawn / copied to the host in a pipeline */
 #define CACHE_THREADS 256
 #define CACHE_LUXCAP 2048
 
@@ -336,7 +337,8 @@ struct Dev
 	int device = 0;
 	char name[256] = "";
 	char err[512] = "";
-	cudaStream_t stream = nullptr;
+	cudaStream_t stream = nullptr, copy = nullptr;
+	cudaEvent_t ev_slice[RC_COPY_SLICES] = {};
 	cudaEvent_t ev[8] = {};
 	uint64_t launches = 0;
 
@@ -471,7 +473,20 @@ int ensure_batch( int nviews, int width, int height )
 }
 
 /* the device stages of one batch on D.stream; ev != NULL -> stage boundaries are recorded */
-int run_stages( bool timed )
+/* span drawing of views [v0, v1) on D.stream */
+int run_draw( int v0, int v1 )
+{
+	rc_work_t &w = D.w;
+	const int32_t chunkcap = rc_draw_chunkcap( w.width );
+	const int nlines = ( v1 - v0 ) * w.height;
+	const int dblocks = ( nlines + DR_WARPS - 1 ) / DR_WARPS;
+	k_draw<<<dblocks < DR_GRID ? dblocks : DR_GRID, DR_WARPS * 32, rc_draw_smem( chunkcap ), D.stream>>>( D.sc, w, chunkcap, v0 * w.height, v1 * w.height );
+	D.launches++;
+	return 0;
+}
+
+/* the device stages of one batch on D.stream; draw_v0 < 0: everything but the span drawing (the caller pipelines it) */
+int run_stages( bool timed, int draw_v0, int draw_v1 )
 {
 	rc_work_t &w = D.w;
 	const rc_scene_t &sc = D.sc;
@@ -509,9 +524,10 @@ int run_stages( bool timed )
 		const int lblocks = ( nlines + LN_WARPS - 1 ) / LN_WARPS;
 		k_lines<<<lblocks < LN_GRID ? lblocks : LN_GRID, LN_WARPS * 32, 0, st>>>( w ); D.launches++;
 		if( timed ) CK( cudaEventRecord( D.ev[4], st ));
-		const int32_t chunkcap = rc_draw_chunkcap( w.width );
-		const int dblocks = ( nlines + DR_WARPS - 1 ) / DR_WARPS;
-		k_draw<<<dblocks < DR_GRID ? dblocks : DR_GRID, DR_WARPS * 32, rc_draw_smem( chunkcap ), st>>>( sc, w, chunkcap ); D.launches++;
+	}
+	if( draw_v0 >= 0 )
+	{
+		if( run_draw( draw_v0, draw_v1 ) != 0 ) return -1;
 	}
 	if( timed ) CK( cudaEventRecord( D.ev[5], st ));
 	CK( cudaGetLastError());
@@ -537,6 +553,8 @@ int rc_dev_init( int device )
 	snprintf( D.name, sizeof( D.name ), "%s (sm_%d%d, %d SMs)", prop.name, prop.major, prop.minor, prop.multiProcessorCount );
 	D.device = device;
 	CK( cudaStreamCreateWithFlags( &D.stream, cudaStreamNonBlocking ));
+	CK( cudaStreamCreateWithFlags( &D.copy, cudaStreamNonBlocking ));
+	for( auto &e : D.ev_slice ) CK( cudaEventCreateWithFlags( &e, cudaEventDisableTiming ));
 	for( auto &e : D.ev ) CK( cudaEventCreate( &e ));
 	CK( cudaFuncSetAttribute( k_viswalk<VW_THREADS_SMALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 64 ));
 	CK( cudaFuncSetAttribute( k_viswalk<VW_THREADS_BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 64 ));
@@ -714,9 +732,29 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 			CK( cudaMemsetAsync( w.zbuf, 0, px * 2, st ));
 		}
 	}
-	if( run_stages( false ) != 0 ) return -1;
-	if( color_out ) CK( cudaMemcpyAsync( color_out, w.color, px * 2, cudaMemcpyDeviceToHost, st ));
-	if( z_out ) CK( cudaMemcpyAsync( z_out, w.zbuf, px * 2, cudaMemcpyDeviceToHost, st ));
+	if( !color_out && !z_out )
+	{
+		if( run_stages( false, 0, nviews ) != 0 ) return -1;
+	}
+	else
+	{
+		/* frames go back to the host: draw the batch in slices of views and copy every slice out on a second
+		 * stream while the next one is drawn (the copies are the long pole of the call: PCIe) */
+		if( run_stages( false, -1, -1 ) != 0 ) return -1;
+		const int nslices = nviews >= 2 * RC_COPY_SLICES ? RC_COPY_SLICES : 1;
+		const size_t vpx = (size_t)width * height;
+		for( int k = 0; k < nslices; k++ )
+		{
+			const int v0 = (int)((long long)nviews * k / nslices ), v1 = (int)((long long)nviews * ( k + 1 ) / nslices );
+			if( run_draw( v0, v1 ) != 0 ) return -1;
+			CK( cudaEventRecord( D.ev_slice[k], st ));
+			CK( cudaStreamWaitEvent( D.copy, D.ev_slice[k], 0 ));
+			if( color_out ) CK( cudaMemcpyAsync( color_out + v0 * vpx, w.color + v0 * vpx, ( v1 - v0 ) * vpx * 2, cudaMemcpyDeviceToHost, D.copy ));
+			if( z_out ) CK( cudaMemcpyAsync( z_out + v0 * vpx, w.zbuf + v0 * vpx, ( v1 - v0 ) * vpx * 2, cudaMemcpyDeviceToHost, D.copy ));
+		}
+		CK( cudaGetLastError());
+		CK( cudaStreamSynchronize( D.copy ));
+	}
 	CK( cudaStreamSynchronize( st ));
 	D.have_batch = true;
 	return 0;
@@ -735,7 +773,7 @@ int rc_dev_bench_resident( int iters, int flags, float *ms_total, float *ms_stag
 			CK( cudaMemsetAsync( D.d_flush, it & 0xFF, flush_bytes, D.stream ));
 		if( flags & RC_BENCH_REBUILD_CACHE )
 			CK( cudaMemsetAsync( D.d_keys, 0, sizeof( rc_cachekey_t ) * (size_t)D.sc.numsurfaces * 4, D.stream ));
-		if( run_stages( true ) != 0 ) return -1;
+		if( run_stages( true, 0, D.w.nviews ) != 0 ) return -1;
 		CK( cudaStreamSynchronize( D.stream ));
 		float ms;
 		CK( cudaEventElapsedTime( &ms, D.ev[0], D.ev[RC_BENCH_STAGES] )); tot += ms;

@@ -53,7 +53,7 @@ __device__ __forceinline__ void rc_texel_at( const rc_surf_t *sf, float sdivz, f
 	*t = rc_clamp_st( rc_f2i( tdivz * z ) + sf->tadjust, sf->bbextentt, lo );
 }
 
-__global__ void __launch_bounds__( DR_WARPS * 32 ) k_draw( rc_scene_t sc, rc_work_t w, int32_t chunkcap )
+__global__ void __launch_bounds__( DR_WARPS * 32 ) k_draw( rc_scene_t sc, rc_work_t w, int32_t chunkcap, int32_t line0, int32_t line1 )
 {
 	extern __shared__ __align__( 16 ) unsigned char smem_raw[];
 	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -63,10 +63,10 @@ __global__ void __launch_bounds__( DR_WARPS * 32 ) k_draw( rc_scene_t sc, rc_wor
 
 	const uint16_t *__restrict__ cache = sc.cache;
 	const uint16_t *__restrict__ texels = sc.texels;
-	const int32_t nlines = w.nviews * w.height, nwarps = gridDim.x * DR_WARPS;
+	const int32_t nwarps = gridDim.x * DR_WARPS; /* lines [line0, line1) of the batch: the host pipelines ranges of views against their copies out */
 	const bool clear = w.clear != 0;
 
-	for( int32_t line = blockIdx.x * DR_WARPS + warp; line < nlines; line += nwarps )
+	for( int32_t line = line0 + blockIdx.x * DR_WARPS + warp; line < line1; line += nwarps )
 	{
 		const rc_lineinfo_t li = w.lineinfo[line];
 		if( li.nsp <= 0 )
