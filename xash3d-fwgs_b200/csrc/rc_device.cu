@@ -477,10 +477,9 @@ int ensure_batch( int nviews, int width, int height )
 int run_draw( int v0, int v1 )
 {
 	rc_work_t &w = D.w;
-	const int32_t chunkcap = rc_draw_chunkcap( w.width );
 	const int nlines = ( v1 - v0 ) * w.height;
 	const int dblocks = ( nlines + DR_WARPS - 1 ) / DR_WARPS;
-	k_draw<<<dblocks < DR_GRID ? dblocks : DR_GRID, DR_WARPS * 32, rc_draw_smem( chunkcap ), D.stream>>>( D.sc, w, chunkcap, v0 * w.height, v1 * w.height );
+	k_draw<<<dblocks < DR_GRID ? dblocks : DR_GRID, DR_WARPS * 32, rc_draw_smem( w.width ), D.stream>>>( D.sc, w, v0 * w.height, v1 * w.height );
 	D.launches++;
 	return 0;
 }
@@ -559,7 +558,7 @@ int rc_dev_init( int device )
 	CK( cudaFuncSetAttribute( k_viswalk<VW_THREADS_SMALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 64 ));
 	CK( cudaFuncSetAttribute( k_viswalk<VW_THREADS_BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 64 ));
 	CK( cudaFuncSetAttribute( k_events, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_events_smem( 65536 / 32 + 2 )));
-	CK( cudaFuncSetAttribute( k_draw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_draw_smem( rc_draw_chunkcap( 4096 ))));
+	CK( cudaFuncSetAttribute( k_draw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_draw_smem( 8192 )));
 	for( int i = 0; i < 256; i++ ) D.h_styles[i] = 256;
 	if( upload( &D.d_styles, D.h_styles, 256 ) != 0 ) return -1;
 	if( dalloc( &D.d_counters, RC_CTR_COUNT ) != 0 ) return -1;
