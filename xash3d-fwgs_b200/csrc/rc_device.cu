@@ -36,6 +36,7 @@ struct rc_cachekey_t
 }; /* 32 B: what D_CacheSurface compares (r_surf.c:1090-1120): texture, light style values */
 
 struct rc_lineinfo_t { int32_t ofs, nsp; }; /* span slice of a scanline: first slot inside the view's arena, count */
+#define RC_LINE_DONE 0x40000000 /* set in nsp by k_lines: the slice holds spans (before: nsp = number of events) */
 
 struct rc_work_t
 {
@@ -53,6 +54,7 @@ struct rc_work_t
 	rc_cachekey_t *cache_keys; /* [numsurfaces * 4] */
 	int32_t   *cache_list;/* [numsurfaces * 4] work list of surf * 4 + mip */
 	int32_t   *cache_nlist, *cache_cursor;
+	int32_t   *line_cursor; /* k_lines work cursor */
 	const int32_t *styles;/* [256] g_lightstylevalue */
 	uint32_t  *scanbits;  /* surface bit sets of k_spans when a view lists > 2015 faces, else NULL */
 	int32_t    scanbits_words, nbands;
@@ -491,12 +493,12 @@ int run_stages( bool timed, int draw_v0, int draw_v1 )
 	const rc_scene_t &sc = D.sc;
 	cudaStream_t st = D.stream;
 	w.cache_need = D.d_need; w.cache_keys = D.d_keys; w.cache_list = D.d_list;
-	w.cache_nlist = D.d_nlist; w.cache_cursor = D.d_nlist + 1;
+	w.cache_nlist = D.d_nlist; w.cache_cursor = D.d_nlist + 1; w.line_cursor = D.d_nlist + 2;
 	w.styles = D.d_styles; w.counters = D.d_counters;
 
 	CK( cudaMemsetAsync( D.d_counters, 0, sizeof( unsigned long long ) * RC_CTR_COUNT, st ));
 	CK( cudaMemsetAsync( D.d_need, 0, sizeof( uint32_t ) * (( sc.numsurfaces * 4 + 31 ) / 32 + 1 ), st ));
-	CK( cudaMemsetAsync( D.d_nlist, 0, sizeof( int32_t ) * 2, st ));
+	CK( cudaMemsetAsync( D.d_nlist, 0, sizeof( int32_t ) * 4, st ));
 	CK( cudaMemsetAsync( w.bandcnt, 0, sizeof( int32_t ) * (size_t)w.nviews * w.nbands, st ));
 	if( timed ) CK( cudaEventRecord( D.ev[0], st ));
 	if( w.vis_stage & VW_STAGE_TREE )
@@ -563,7 +565,7 @@ int rc_dev_init( int device )
 	if( upload( &D.d_styles, D.h_styles, 256 ) != 0 ) return -1;
 	if( dalloc( &D.d_counters, RC_CTR_COUNT ) != 0 ) return -1;
 	CK( cudaMemset( D.d_counters, 0, sizeof( unsigned long long ) * RC_CTR_COUNT ));
-	if( dalloc( &D.d_nlist, 2 ) != 0 ) return -1;
+	if( dalloc( &D.d_nlist, 4 ) != 0 ) return -1;
 	D.ready = true;
 	return 0;
 }

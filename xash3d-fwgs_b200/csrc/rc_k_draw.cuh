@@ -85,7 +85,10 @@ __global__ void __launch_bounds__( DR_WARPS * 32 ) k_draw( rc_scene_t sc, rc_wor
 
 	for( int32_t line = line0 + blockIdx.x * DR_WARPS + warp; line < line1; line += nwarps )
 	{
-		const rc_lineinfo_t li = w.lineinfo[line];
+		rc_lineinfo_t li = w.lineinfo[line];
+		if( !( li.nsp & RC_LINE_DONE ))
+			continue;
+		li.nsp &= ~RC_LINE_DONE;
 		if( li.nsp <= 0 )
 			continue;
 		const int32_t view = line / w.height, y = line - view * w.height;

@@ -23,6 +23,8 @@
 #define EV_THREADS  256
 #define EV_WARPS    ( EV_THREADS / 32 )
 #define LN_WARPS    4
+#define LN_HEAVY    64   /* events: lines above go first */
+#define LN_CHUNK    4    /* scanlines a warp takes from the shared cursor at a time */
 #define SP_SORTCAP  512  /* events per line the shared-memory sorter takes; longer lines fall back to a serial sort */
 #define SP_BITWORDS 64   /* shared-memory bit-set words per line (views listing <= 2015 faces), else global scratch */
 #define SP_EXCCAP   8
@@ -320,13 +322,14 @@ __device__ __forceinline__ int32_t rc_replay_warp( const unsigned long long *key
 	return nspans;
 }
 
-__global__ void __launch_bounds__( LN_WARPS * 32 ) k_lines( rc_work_t w )
+__global__ void __launch_bounds__( LN_WARPS * 32, 8 ) k_lines( rc_work_t w )
 {
 	__shared__ __align__( 16 ) unsigned long long s_keys[LN_WARPS][SP_SORTCAP];
 	__shared__ uint32_t s_bits[LN_WARPS][SP_BITWORDS + 1];
 
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-	const int32_t gwarp = blockIdx.x * LN_WARPS + warp, nwarps = gridDim.x * LN_WARPS;
+	const int32_t gwarp = blockIdx.x * LN_WARPS + warp;
+	int32_t cur = 0;
 	const int32_t nlines = w.nviews * w.height;
 	unsigned long long *keys = s_keys[warp];
 	int32_t nspans_total = 0, novf = 0, nserial = 0, nsorted = 0;
@@ -334,15 +337,37 @@ __global__ void __launch_bounds__( LN_WARPS * 32 ) k_lines( rc_work_t w )
 	const long long dbg_start = clock64();
 #endif
 
-	for( int32_t line = gwarp; line < nlines; line += nwarps )
+	/* scanlines differ a lot in cost (2 .. 500 events) and the heavy ones cluster (the horizon of corridor views):
+	 * warps draw them from a shared cursor, view-interleaved */
+	/* two sweeps over the lines: the heavy ones first (longest processing time first keeps the tail short) */
+	for( int32_t q = 0, heavy = 1; ; q++ )
 	{
-		const int32_t view = line / w.height;
+		int32_t item = 0;
+		if(( q & ( LN_CHUNK - 1 )) == 0 )
+		{
+			if( lane == 0 ) item = atomicAdd( w.line_cursor + ( heavy ? 0 : 1 ), LN_CHUNK );
+			cur = __shfl_sync( 0xFFFFFFFFu, item, 0 );
+		}
+		item = cur + ( q & ( LN_CHUNK - 1 ));
+		if( cur >= nlines )
+		{
+			if( !heavy )
+				break;
+			heavy = 0; q = -1;
+			continue;
+		}
+		if( item >= nlines )
+			continue;
+		const int32_t view = item % w.nviews;
+		const int32_t line = view * w.height + item / w.nviews;
 		const rc_lineinfo_t li = w.lineinfo[line];
 		if( li.ofs < 0 )
 			continue;
+		const int32_t n = li.nsp;
+		if(( n & RC_LINE_DONE ) || ( n > LN_HEAVY ) != ( heavy != 0 ))
+			continue; /* done in the first sweep, or the other sweep's line */
 		const rc_view_t *vw = &w.views[view];
 		const int32_t x0 = vw->vrect[0], vw_w = vw->vrect[2];
-		const int32_t n = li.nsp;
 #ifdef RC_SPANS_DEBUG
 		const long long dbg0 = clock64();
 #endif
@@ -471,7 +496,7 @@ __global__ void __launch_bounds__( LN_WARPS * 32 ) k_lines( rc_work_t w )
 		}
 		if( lane == 0 )
 		{
-			w.lineinfo[line].nsp = nsp;
+			w.lineinfo[line].nsp = nsp | RC_LINE_DONE;
 			nspans_total += nsp;
 		}
 		__syncwarp();
