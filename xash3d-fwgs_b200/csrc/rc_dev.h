@@ -43,6 +43,7 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
  * report CUDA-event milliseconds: total and per stage (vis+walk, faces, cache, spans, draw) */
 #define RC_BENCH_REBUILD_CACHE 1 /* invalidate every cache block before each iteration (config C3 behaviour) */
 #define RC_BENCH_FLUSH_L2      2 /* write 256 MB between iterations, outside the timed region */
+#define RC_BENCH_OVERLAP       4 /* run the batch as rc_dev_render does for host outputs: 4 view slices on 2 streams (total only) */
 #define RC_BENCH_STAGES        5 /* vis+walk, faces, cache, spans, draw */
 int rc_dev_bench_resident( int iters, int flags, float *ms_total, float *ms_stage /* [RC_BENCH_STAGES] */ );
 

@@ -73,7 +73,7 @@ struct rc_work_t
 
 #define SP_LINES 32 /* scanlines per band (rc_k_spans.cuh): k_faces bins edges by band */
 #define LN_GRID  ( 148 * 12 ) /* k_lines blocks: 12 resident blocks of 4 warps per SM */
-#define RC_COPY_SLICES 8 /* rc_dev_render: view slices drawn / copied to the host in a pipeline */
+#define RC_MAX_SLICES 4 /* view slices of a batch that run on concurrent streams */
 #define CACHE_THREADS 256
 #define CACHE_LUXCAP 2048
 
@@ -312,6 +312,9 @@ __global__ void __launch_bounds__( CACHE_THREADS ) k_cache_build( rc_scene_t sc,
 		else if( mip == 2 ) rc_cache_runs<4>( sc, tex, mip, s_bl, smax, s_rc, nbu, dst, bw, bh, tid );
 		else rc_cache_runs<2>( sc, tex, mip, s_bl, smax, s_rc, nbu, dst, bw, bh, tid );
 
+		/* another slice's stream may test this key while the block is being written: publish it only after the texels */
+		__threadfence();
+		__syncthreads();
 		if( tid == 0 )
 		{
 			rc_cachekey_t *kk = &w.cache_keys[slot];
@@ -340,7 +343,8 @@ struct Dev
 	char name[256] = "";
 	char err[512] = "";
 	cudaStream_t stream = nullptr, copy = nullptr;
-	cudaEvent_t ev_slice[RC_COPY_SLICES] = {};
+	cudaStream_t slice_stream[RC_MAX_SLICES] = {};
+	cudaEvent_t ev_slice[RC_MAX_SLICES] = {}, ev_fork = nullptr;
 	cudaEvent_t ev[8] = {};
 	uint64_t launches = 0;
 
@@ -456,7 +460,7 @@ int ensure_batch( int nviews, int width, int height )
 	w.view_events = (size_t)w.nbands * w.blk_events;
 	w.scanbits = nullptr; w.scanbits_words = ( w.max_cands + 32 ) / 32;
 	if( w.scanbits_words > SP_BITWORDS )
-		WALLOC( scanbits, uint32_t, (size_t)LN_GRID * LN_WARPS * w.scanbits_words );
+		WALLOC( scanbits, uint32_t, (size_t)RC_MAX_SLICES * LN_GRID * LN_WARPS * w.scanbits_words );
 	WALLOC( bandcnt, int32_t, (size_t)cap * w.nbands );
 	WALLOC( bandedges, rc_edge_t, (size_t)cap * w.nbands * w.band_cap );
 	WALLOC( bandsurf, uint16_t, (size_t)cap * w.nbands * ( (size_t)w.band_cap + 2 ));
@@ -475,62 +479,116 @@ int ensure_batch( int nviews, int width, int height )
 }
 
 /* the device stages of one batch on D.stream; ev != NULL -> stage boundaries are recorded */
-/* span drawing of views [v0, v1) on D.stream */
-int run_draw( int v0, int v1 )
+/* the batch work record restricted to views [v0, v1): every per-view array starts at v0; slice k owns its own cache
+ * work list, cursors and bit-set scratch so that slices can run on different streams at the same time */
+rc_work_t make_slice( int k, int v0, int v1 )
 {
-	rc_work_t &w = D.w;
-	const int nlines = ( v1 - v0 ) * w.height;
-	const int dblocks = ( nlines + DR_WARPS - 1 ) / DR_WARPS;
-	k_draw<<<dblocks < DR_GRID ? dblocks : DR_GRID, DR_WARPS * 32, rc_draw_smem( w.width ), D.stream>>>( D.sc, w, v0 * w.height, v1 * w.height );
+	rc_work_t ws = D.w;
+	const rc_scene_t &sc = D.sc;
+	const size_t nslots = (size_t)sc.numsurfaces * 4;
+	ws.nviews = v1 - v0;
+	ws.views += v0;
+	ws.walkstack += (size_t)v0 * ws.stack_ints;
+	ws.cands += (size_t)v0 * ws.max_cands; ws.surfs += (size_t)v0 * ws.max_cands;
+	ws.edges += (size_t)v0 * ws.max_edges;
+	ws.ncands += v0; ws.nedges += v0;
+	ws.bandcnt += (size_t)v0 * ws.nbands; ws.bandnloc += (size_t)v0 * ws.nbands;
+	ws.bandedges += (size_t)v0 * ws.nbands * ws.band_cap;
+	ws.bandsurf += (size_t)v0 * ws.nbands * ( (size_t)ws.band_cap + 2 );
+	ws.events += (size_t)v0 * ws.view_events;
+	ws.lineinfo += (size_t)v0 * ws.height;
+	ws.color += (size_t)v0 * ws.width * ws.height; ws.zbuf += (size_t)v0 * ws.width * ws.height;
+	if( ws.scanbits ) ws.scanbits += (size_t)k * LN_GRID * LN_WARPS * ws.scanbits_words;
+	ws.cache_need = D.d_need + (size_t)k * ( nslots / 32 + 2 );
+	ws.cache_keys = D.d_keys;
+	ws.cache_list = D.d_list + (size_t)k * nslots;
+	ws.cache_nlist = D.d_nlist + 4 * k; ws.cache_cursor = ws.cache_nlist + 1; ws.line_cursor = ws.cache_nlist + 2;
+	ws.styles = D.d_styles; ws.counters = D.d_counters;
+	return ws;
+}
+
+/* all stages of one slice on stream st; evs != NULL: stage boundaries are recorded there */
+int launch_slice( const rc_work_t &ws, cudaStream_t st, cudaEvent_t *evs, bool draw )
+{
+	const rc_scene_t &sc = D.sc;
+	CK( cudaMemsetAsync( ws.cache_need, 0, sizeof( uint32_t ) * (( sc.numsurfaces * 4 + 31 ) / 32 + 1 ), st ));
+	CK( cudaMemsetAsync( ws.cache_nlist, 0, sizeof( int32_t ) * 4, st ));
+	CK( cudaMemsetAsync( ws.bandcnt, 0, sizeof( int32_t ) * (size_t)ws.nviews * ws.nbands, st ));
+	if( evs ) CK( cudaEventRecord( evs[0], st ));
+	if( ws.vis_stage & VW_STAGE_TREE )
+		k_viswalk<VW_THREADS_SMALL><<<ws.nviews, VW_THREADS_SMALL, (size_t)ws.vis_smem, st>>>( sc, ws );
+	else
+		k_viswalk<VW_THREADS_BIG><<<ws.nviews, VW_THREADS_BIG, (size_t)ws.vis_smem, st>>>( sc, ws );
 	D.launches++;
+	if( evs ) CK( cudaEventRecord( evs[1], st ));
+	{
+		dim3 g(( ws.max_cands + 127 ) / 128, ws.nviews );
+		k_faces<<<g, 128, 0, st>>>( sc, ws ); D.launches++;
+	}
+	if( evs ) CK( cudaEventRecord( evs[2], st ));
+	{
+		int nslots = sc.numsurfaces * 4;
+		k_cache_list<<<( nslots + 255 ) / 256, 256, 0, st>>>( sc, ws ); D.launches++;
+		k_cache_build<<<148 * 4, CACHE_THREADS, 0, st>>>( sc, ws ); D.launches++;
+	}
+	if( evs ) CK( cudaEventRecord( evs[3], st ));
+	const int nlines = ws.nviews * ws.height;
+	{
+		dim3 g( ws.nbands, ws.nviews );
+		k_events<<<g, EV_THREADS, rc_events_smem( ws.scanbits_words ), st>>>( ws ); D.launches++;
+		const int lblocks = ( nlines + LN_WARPS - 1 ) / LN_WARPS;
+		k_lines<<<lblocks < LN_GRID ? lblocks : LN_GRID, LN_WARPS * 32, 0, st>>>( ws ); D.launches++;
+	}
+	if( evs ) CK( cudaEventRecord( evs[4], st ));
+	if( draw )
+	{
+		const int dblocks = ( nlines + DR_WARPS - 1 ) / DR_WARPS;
+		k_draw<<<dblocks < DR_GRID ? dblocks : DR_GRID, DR_WARPS * 32, rc_draw_smem( ws.width ), st>>>( sc, ws, 0, nlines );
+		D.launches++;
+	}
+	if( evs ) CK( cudaEventRecord( evs[5], st ));
 	return 0;
 }
 
-/* the device stages of one batch on D.stream; draw_v0 < 0: everything but the span drawing (the caller pipelines it) */
-int run_stages( bool timed, int draw_v0, int draw_v1 )
+/*
+ * The device stages of the batch.  nslices == 1: one stream, stage boundaries optionally recorded in D.ev (the
+ * per-kernel timings of the bench).  nslices > 1: the views are cut into slices, slice k on stream k % nstreams;
+ * with host outputs (color_out / z_out) every slice's frames are copied out on D.copy as soon as the slice is drawn.
+ */
+int run_batch( int nslices, int nstreams, bool timed, uint16_t *color_out, int16_t *z_out )
 {
 	rc_work_t &w = D.w;
-	const rc_scene_t &sc = D.sc;
 	cudaStream_t st = D.stream;
-	w.cache_need = D.d_need; w.cache_keys = D.d_keys; w.cache_list = D.d_list;
-	w.cache_nlist = D.d_nlist; w.cache_cursor = D.d_nlist + 1; w.line_cursor = D.d_nlist + 2;
-	w.styles = D.d_styles; w.counters = D.d_counters;
-
+	const size_t vpx = (size_t)w.width * w.height;
 	CK( cudaMemsetAsync( D.d_counters, 0, sizeof( unsigned long long ) * RC_CTR_COUNT, st ));
-	CK( cudaMemsetAsync( D.d_need, 0, sizeof( uint32_t ) * (( sc.numsurfaces * 4 + 31 ) / 32 + 1 ), st ));
-	CK( cudaMemsetAsync( D.d_nlist, 0, sizeof( int32_t ) * 4, st ));
-	CK( cudaMemsetAsync( w.bandcnt, 0, sizeof( int32_t ) * (size_t)w.nviews * w.nbands, st ));
+	if( nslices <= 1 )
+	{
+		const rc_work_t ws = make_slice( 0, 0, w.nviews );
+		if( launch_slice( ws, st, timed ? D.ev : nullptr, true ) != 0 ) return -1;
+		if( color_out ) CK( cudaMemcpyAsync( color_out, w.color, (size_t)w.nviews * vpx * 2, cudaMemcpyDeviceToHost, st ));
+		if( z_out ) CK( cudaMemcpyAsync( z_out, w.zbuf, (size_t)w.nviews * vpx * 2, cudaMemcpyDeviceToHost, st ));
+		CK( cudaGetLastError());
+		return 0;
+	}
 	if( timed ) CK( cudaEventRecord( D.ev[0], st ));
-	if( w.vis_stage & VW_STAGE_TREE )
-		k_viswalk<VW_THREADS_SMALL><<<w.nviews, VW_THREADS_SMALL, (size_t)w.vis_smem, st>>>( sc, w );
-	else
-		k_viswalk<VW_THREADS_BIG><<<w.nviews, VW_THREADS_BIG, (size_t)w.vis_smem, st>>>( sc, w );
-	D.launches++;
-	if( timed ) CK( cudaEventRecord( D.ev[1], st ));
+	CK( cudaEventRecord( D.ev_fork, st ));
+	for( int p = 0; p < nstreams; p++ ) CK( cudaStreamWaitEvent( D.slice_stream[p], D.ev_fork, 0 ));
+	for( int k = 0; k < nslices; k++ )
 	{
-		dim3 g(( w.max_cands + 127 ) / 128, w.nviews );
-		k_faces<<<g, 128, 0, st>>>( sc, w ); D.launches++;
+		const int v0 = (int)((long long)w.nviews * k / nslices ), v1 = (int)((long long)w.nviews * ( k + 1 ) / nslices );
+		cudaStream_t ss = D.slice_stream[k % nstreams];
+		const rc_work_t ws = make_slice( k, v0, v1 );
+		if( launch_slice( ws, ss, nullptr, true ) != 0 ) return -1;
+		CK( cudaEventRecord( D.ev_slice[k], ss ));
+		if( color_out || z_out )
+		{
+			CK( cudaStreamWaitEvent( D.copy, D.ev_slice[k], 0 ));
+			if( color_out ) CK( cudaMemcpyAsync( color_out + v0 * vpx, w.color + v0 * vpx, ( v1 - v0 ) * vpx * 2, cudaMemcpyDeviceToHost, D.copy ));
+			if( z_out ) CK( cudaMemcpyAsync( z_out + v0 * vpx, w.zbuf + v0 * vpx, ( v1 - v0 ) * vpx * 2, cudaMemcpyDeviceToHost, D.copy ));
+		}
+		CK( cudaStreamWaitEvent( st, D.ev_slice[k], 0 ));
 	}
-	if( timed ) CK( cudaEventRecord( D.ev[2], st ));
-	{
-		int nslots = sc.numsurfaces * 4;
-		k_cache_list<<<( nslots + 255 ) / 256, 256, 0, st>>>( sc, w ); D.launches++;
-		k_cache_build<<<148 * 4, CACHE_THREADS, 0, st>>>( sc, w ); D.launches++;
-	}
-	if( timed ) CK( cudaEventRecord( D.ev[3], st ));
-	{
-		dim3 g( w.nbands, w.nviews );
-		k_events<<<g, EV_THREADS, rc_events_smem( w.scanbits_words ), st>>>( w ); D.launches++;
-		const int nlines = w.nviews * w.height;
-		const int lblocks = ( nlines + LN_WARPS - 1 ) / LN_WARPS;
-		k_lines<<<lblocks < LN_GRID ? lblocks : LN_GRID, LN_WARPS * 32, 0, st>>>( w ); D.launches++;
-		if( timed ) CK( cudaEventRecord( D.ev[4], st ));
-	}
-	if( draw_v0 >= 0 )
-	{
-		if( run_draw( draw_v0, draw_v1 ) != 0 ) return -1;
-	}
-	if( timed ) CK( cudaEventRecord( D.ev[5], st ));
+	if( timed ) CK( cudaEventRecord( D.ev[RC_BENCH_STAGES], st ));
 	CK( cudaGetLastError());
 	return 0;
 }
@@ -556,6 +614,8 @@ int rc_dev_init( int device )
 	CK( cudaStreamCreateWithFlags( &D.stream, cudaStreamNonBlocking ));
 	CK( cudaStreamCreateWithFlags( &D.copy, cudaStreamNonBlocking ));
 	for( auto &e : D.ev_slice ) CK( cudaEventCreateWithFlags( &e, cudaEventDisableTiming ));
+	CK( cudaEventCreateWithFlags( &D.ev_fork, cudaEventDisableTiming ));
+	for( auto &ss : D.slice_stream ) CK( cudaStreamCreateWithFlags( &ss, cudaStreamNonBlocking ));
 	for( auto &e : D.ev ) CK( cudaEventCreate( &e ));
 	CK( cudaFuncSetAttribute( k_viswalk<VW_THREADS_SMALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 64 ));
 	CK( cudaFuncSetAttribute( k_viswalk<VW_THREADS_BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 64 ));
@@ -565,7 +625,7 @@ int rc_dev_init( int device )
 	if( upload( &D.d_styles, D.h_styles, 256 ) != 0 ) return -1;
 	if( dalloc( &D.d_counters, RC_CTR_COUNT ) != 0 ) return -1;
 	CK( cudaMemset( D.d_counters, 0, sizeof( unsigned long long ) * RC_CTR_COUNT ));
-	if( dalloc( &D.d_nlist, 4 ) != 0 ) return -1;
+	if( dalloc( &D.d_nlist, 4 * RC_MAX_SLICES ) != 0 ) return -1;
 	D.ready = true;
 	return 0;
 }
@@ -676,8 +736,8 @@ int rc_dev_upload_scene( const rc_scene_t *sc, size_t cache_texels )
 
 	size_t nslots = (size_t)sc->numsurfaces * 4;
 	if( upload( &D.d_keys, (const rc_cachekey_t *)nullptr, nslots ) != 0 ) return -1;
-	if( upload( &D.d_need, (const uint32_t *)nullptr, nslots / 32 + 2 ) != 0 ) return -1;
-	if( upload( &D.d_list, (const int32_t *)nullptr, nslots ) != 0 ) return -1;
+	if( upload( &D.d_need, (const uint32_t *)nullptr, RC_MAX_SLICES * ( nslots / 32 + 2 )) != 0 ) return -1;
+	if( upload( &D.d_list, (const int32_t *)nullptr, RC_MAX_SLICES * nslots ) != 0 ) return -1;
 	return 0;
 }
 
@@ -733,28 +793,15 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 			CK( cudaMemsetAsync( w.zbuf, 0, px * 2, st ));
 		}
 	}
-	if( !color_out && !z_out )
 	{
-		if( run_stages( false, 0, nviews ) != 0 ) return -1;
-	}
-	else
-	{
-		/* frames go back to the host: draw the batch in slices of views and copy every slice out on a second
-		 * stream while the next one is drawn (the copies are the long pole of the call: PCIe) */
-		if( run_stages( false, -1, -1 ) != 0 ) return -1;
-		const int nslices = nviews >= 2 * RC_COPY_SLICES ? RC_COPY_SLICES : 1;
-		const size_t vpx = (size_t)width * height;
-		for( int k = 0; k < nslices; k++ )
-		{
-			const int v0 = (int)((long long)nviews * k / nslices ), v1 = (int)((long long)nviews * ( k + 1 ) / nslices );
-			if( run_draw( v0, v1 ) != 0 ) return -1;
-			CK( cudaEventRecord( D.ev_slice[k], st ));
-			CK( cudaStreamWaitEvent( D.copy, D.ev_slice[k], 0 ));
-			if( color_out ) CK( cudaMemcpyAsync( color_out + v0 * vpx, w.color + v0 * vpx, ( v1 - v0 ) * vpx * 2, cudaMemcpyDeviceToHost, D.copy ));
-			if( z_out ) CK( cudaMemcpyAsync( z_out + v0 * vpx, w.zbuf + v0 * vpx, ( v1 - v0 ) * vpx * 2, cudaMemcpyDeviceToHost, D.copy ));
-		}
-		CK( cudaGetLastError());
-		CK( cudaStreamSynchronize( D.copy ));
+		/* frames that go back to the host: 4 slices of views on two streams, so that the copies of the first pair
+		 * overlap the stages of the second (the copies are the long pole: PCIe).  Frames that stay in HBM: one
+		 * stream - running the slices side by side was measured and gains nothing (every kernel already exposes the
+		 * whole batch's parallelism; the slices move in lockstep) */
+		const bool out = color_out || z_out;
+		const int nslices = out && nviews >= 16 * RC_MAX_SLICES ? RC_MAX_SLICES : 1;
+		if( run_batch( nslices, 2, false, color_out, z_out ) != 0 ) return -1;
+		if( out && nslices > 1 ) CK( cudaStreamSynchronize( D.copy ));
 	}
 	CK( cudaStreamSynchronize( st ));
 	D.have_batch = true;
@@ -765,6 +812,7 @@ int rc_dev_bench_resident( int iters, int flags, float *ms_total, float *ms_stag
 {
 	if( !D.have_batch ) { snprintf( D.err, sizeof( D.err ), "no batch rendered yet" ); return -1; }
 	float tot = 0, stage[RC_BENCH_STAGES] = { 0 };
+	bool overlapped = false;
 	const size_t flush_bytes = (size_t)256 << 20; /* > 126 MB of L2 */
 	if(( flags & RC_BENCH_FLUSH_L2 ) && !D.d_flush )
 		CK( cudaMalloc( &D.d_flush, flush_bytes ));
@@ -774,11 +822,15 @@ int rc_dev_bench_resident( int iters, int flags, float *ms_total, float *ms_stag
 			CK( cudaMemsetAsync( D.d_flush, it & 0xFF, flush_bytes, D.stream ));
 		if( flags & RC_BENCH_REBUILD_CACHE )
 			CK( cudaMemsetAsync( D.d_keys, 0, sizeof( rc_cachekey_t ) * (size_t)D.sc.numsurfaces * 4, D.stream ));
-		if( run_stages( true, 0, D.w.nviews ) != 0 ) return -1;
+		{
+			const bool overlap = ( flags & RC_BENCH_OVERLAP ) && D.w.nviews >= 16 * RC_MAX_SLICES;
+			if( run_batch( overlap ? RC_MAX_SLICES : 1, 2, true, nullptr, nullptr ) != 0 ) return -1;
+			if( overlap ) overlapped = true;
+		}
 		CK( cudaStreamSynchronize( D.stream ));
 		float ms;
 		CK( cudaEventElapsedTime( &ms, D.ev[0], D.ev[RC_BENCH_STAGES] )); tot += ms;
-		for( int s = 0; s < RC_BENCH_STAGES; s++ ) { CK( cudaEventElapsedTime( &ms, D.ev[s], D.ev[s + 1] )); stage[s] += ms; }
+		if( !overlapped ) for( int s = 0; s < RC_BENCH_STAGES; s++ ) { CK( cudaEventElapsedTime( &ms, D.ev[s], D.ev[s + 1] )); stage[s] += ms; }
 	}
 	if( ms_total ) *ms_total = tot / ( iters > 0 ? iters : 1 );
 	if( ms_stage ) for( int s = 0; s < RC_BENCH_STAGES; s++ ) ms_stage[s] = stage[s] / ( iters > 0 ? iters : 1 );
