@@ -58,11 +58,10 @@ struct rc_work_t
 	const int32_t *styles;/* [256] g_lightstylevalue */
 	uint32_t  *scanbits;  /* surface bit sets of k_spans when a view lists > 2015 faces, else NULL */
 	int32_t    scanbits_words, nbands;
-	int32_t   *bandcnt;   /* [nviews][nbands] edges binned per band of SP_LINES scanlines */
-	rc_edge_t *bandedges; /* [nviews][nbands][band_cap] */
-	uint16_t  *bandsurf;  /* [nviews][nbands][band_cap + 2] band-local surface number -> candidate index + 1 */
+	uint16_t  *bandsurf;  /* [nviews][nbands][max_cands + 2] band-local surface number -> candidate index + 1 */
 	int32_t   *bandnloc;  /* [nviews][nbands] surfaces present in the band */
-	int32_t    band_cap, blk_events; /* capacities: edges per band, event/span slots per band */
+	int32_t    blk_events;           /* capacity: event/span slots per band */
+	int32_t    ev_ecap;              /* band edges k_events stages in shared memory */
 	size_t     view_events;          /* nbands * blk_events */
 	unsigned long long *events;      /* [nviews][nbands][blk_events] sort keys, then rc_span_t in place */
 	rc_lineinfo_t *lineinfo;         /* [nviews][height] span slice of every scanline */
@@ -115,6 +114,12 @@ __global__ void __launch_bounds__( 128 ) k_faces( rc_scene_t sc, rc_work_t w )
 	fs.surfnum = (uint32_t)ci + 1;
 	if( first + want > w.max_edges )
 	{
+		/* the part of the reservation that is inside the list must not stay uninitialised: k_events reads all of it */
+		for( int32_t k = first; k < w.max_edges; k++ )
+		{
+			rc_edge_t *ne = w.edges + (size_t)view * w.max_edges + k;
+			ne->u = 0; ne->u_step = 0; ne->vv = 1u; ne->surfs = 0;
+		}
 		fs.maxout = 0;
 		atomicAdd( &w.counters[RC_CTR_OVERFLOW_EDGES], 1ull );
 	}
@@ -128,21 +133,6 @@ __global__ void __launch_bounds__( 128 ) k_faces( rc_scene_t sc, rc_work_t w )
 	*out = o;
 
 	int32_t nout = fs.nout < fs.maxout ? fs.nout : fs.maxout;
-	/* every edge also goes to the list of each band of SP_LINES scanlines it crosses (k_spans reads those) */
-	for( int32_t k = 0; k < nout; k++ )
-	{
-		const rc_edge_t e = fs.out[k];
-		int32_t v = (int32_t)( e.vv & 0xFFFF ), v2 = (int32_t)( e.vv >> 16 );
-		if( v2 >= w.height ) v2 = w.height - 1;
-		for( int32_t b = v / SP_LINES; b <= v2 / SP_LINES; b++ )
-		{
-			const int32_t slot = atomicAdd( &w.bandcnt[view * w.nbands + b], 1 );
-			if( slot < w.band_cap )
-				w.bandedges[((size_t)view * w.nbands + b ) * w.band_cap + slot] = e;
-			else if( slot == w.band_cap )
-				atomicAdd( &w.counters[RC_CTR_OVERFLOW_EDGES], 1ull );
-		}
-	}
 	/* unused reservations become edges that are never active */
 	for( int32_t k = nout; k < fs.maxout; k++ )
 	{
@@ -455,15 +445,13 @@ int ensure_batch( int nviews, int width, int height )
 	WALLOC( ncands, int32_t, cap );
 	WALLOC( nedges, int32_t, cap );
 	w.nbands = ( height + SP_LINES - 1 ) / SP_LINES;
-	w.band_cap = w.max_edges / 2 < 1024 ? 1024 : ( w.max_edges / 2 > 32768 ? 32768 : w.max_edges / 2 );
+	w.ev_ecap = width * height <= 640 * 480 ? 2048 : 4096;
 	w.blk_events = SP_LINES * ( width / 2 > 512 ? width / 2 : 512 );
 	w.view_events = (size_t)w.nbands * w.blk_events;
 	w.scanbits = nullptr; w.scanbits_words = ( w.max_cands + 32 ) / 32;
 	if( w.scanbits_words > SP_BITWORDS )
 		WALLOC( scanbits, uint32_t, (size_t)RC_MAX_SLICES * LN_GRID * LN_WARPS * w.scanbits_words );
-	WALLOC( bandcnt, int32_t, (size_t)cap * w.nbands );
-	WALLOC( bandedges, rc_edge_t, (size_t)cap * w.nbands * w.band_cap );
-	WALLOC( bandsurf, uint16_t, (size_t)cap * w.nbands * ( (size_t)w.band_cap + 2 ));
+	WALLOC( bandsurf, uint16_t, (size_t)cap * w.nbands * ( (size_t)w.max_cands + 2 ));
 	WALLOC( bandnloc, int32_t, (size_t)cap * w.nbands );
 	WALLOC( events, unsigned long long, (size_t)cap * w.view_events );
 	WALLOC( lineinfo, rc_lineinfo_t, (size_t)cap * height );
@@ -492,9 +480,8 @@ rc_work_t make_slice( int k, int v0, int v1 )
 	ws.cands += (size_t)v0 * ws.max_cands; ws.surfs += (size_t)v0 * ws.max_cands;
 	ws.edges += (size_t)v0 * ws.max_edges;
 	ws.ncands += v0; ws.nedges += v0;
-	ws.bandcnt += (size_t)v0 * ws.nbands; ws.bandnloc += (size_t)v0 * ws.nbands;
-	ws.bandedges += (size_t)v0 * ws.nbands * ws.band_cap;
-	ws.bandsurf += (size_t)v0 * ws.nbands * ( (size_t)ws.band_cap + 2 );
+	ws.bandnloc += (size_t)v0 * ws.nbands;
+	ws.bandsurf += (size_t)v0 * ws.nbands * ( (size_t)ws.max_cands + 2 );
 	ws.events += (size_t)v0 * ws.view_events;
 	ws.lineinfo += (size_t)v0 * ws.height;
 	ws.color += (size_t)v0 * ws.width * ws.height; ws.zbuf += (size_t)v0 * ws.width * ws.height;
@@ -513,12 +500,8 @@ int launch_slice( const rc_work_t &ws, cudaStream_t st, cudaEvent_t *evs, bool d
 	const rc_scene_t &sc = D.sc;
 	CK( cudaMemsetAsync( ws.cache_need, 0, sizeof( uint32_t ) * (( sc.numsurfaces * 4 + 31 ) / 32 + 1 ), st ));
 	CK( cudaMemsetAsync( ws.cache_nlist, 0, sizeof( int32_t ) * 4, st ));
-	CK( cudaMemsetAsync( ws.bandcnt, 0, sizeof( int32_t ) * (size_t)ws.nviews * ws.nbands, st ));
 	if( evs ) CK( cudaEventRecord( evs[0], st ));
-	if( ws.vis_stage & VW_STAGE_TREE )
-		k_viswalk<VW_THREADS_SMALL><<<ws.nviews, VW_THREADS_SMALL, (size_t)ws.vis_smem, st>>>( sc, ws );
-	else
-		k_viswalk<VW_THREADS_BIG><<<ws.nviews, VW_THREADS_BIG, (size_t)ws.vis_smem, st>>>( sc, ws );
+	k_viswalk<VW_NTHREADS><<<ws.nviews, VW_NTHREADS, (size_t)ws.vis_smem, st>>>( sc, ws );
 	D.launches++;
 	if( evs ) CK( cudaEventRecord( evs[1], st ));
 	{
@@ -535,7 +518,7 @@ int launch_slice( const rc_work_t &ws, cudaStream_t st, cudaEvent_t *evs, bool d
 	const int nlines = ws.nviews * ws.height;
 	{
 		dim3 g( ws.nbands, ws.nviews );
-		k_events<<<g, EV_THREADS, rc_events_smem( ws.scanbits_words ), st>>>( ws ); D.launches++;
+		k_events<<<g, EV_THREADS, rc_events_smem( ws.ev_ecap, ws.scanbits_words ), st>>>( ws ); D.launches++;
 		const int lblocks = ( nlines + LN_WARPS - 1 ) / LN_WARPS;
 		k_lines<<<lblocks < LN_GRID ? lblocks : LN_GRID, LN_WARPS * 32, 0, st>>>( ws ); D.launches++;
 	}
@@ -617,9 +600,8 @@ int rc_dev_init( int device )
 	CK( cudaEventCreateWithFlags( &D.ev_fork, cudaEventDisableTiming ));
 	for( auto &ss : D.slice_stream ) CK( cudaStreamCreateWithFlags( &ss, cudaStreamNonBlocking ));
 	for( auto &e : D.ev ) CK( cudaEventCreate( &e ));
-	CK( cudaFuncSetAttribute( k_viswalk<VW_THREADS_SMALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 64 ));
-	CK( cudaFuncSetAttribute( k_viswalk<VW_THREADS_BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 64 ));
-	CK( cudaFuncSetAttribute( k_events, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_events_smem( 65536 / 32 + 2 )));
+	CK( cudaFuncSetAttribute( k_viswalk<VW_NTHREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 64 ));
+	CK( cudaFuncSetAttribute( k_events, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_events_smem( EV_ECAP_MAX, 65536 / 32 + 2 )));
 	CK( cudaFuncSetAttribute( k_draw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_draw_smem( 8192 )));
 	for( int i = 0; i < 256; i++ ) D.h_styles[i] = 256;
 	if( upload( &D.d_styles, D.h_styles, 256 ) != 0 ) return -1;

@@ -34,11 +34,13 @@
 #error "k_events maps lanes to scanlines: SP_LINES must be 32"
 #endif
 
-#define EV_ECAP 2048 /* band edges staged and pre-sorted in shared memory; longer lists are read from HBM unsorted */
+/* band edges staged and pre-sorted in shared memory: w.ev_ecap of them (2048 for small frames, 4096 for big ones, where
+ * a band of 32 lines is crossed by more edges); longer lists are read from the view's edge list in HBM, unsorted */
+#define EV_ECAP_MAX 8192 /* 13 bits of the presort key */
 
-static inline size_t rc_events_smem( int32_t bitwords )
+static inline size_t rc_events_smem( int32_t ecap, int32_t bitwords )
 {
-	return sizeof( rc_edge_t ) * EV_ECAP + sizeof( unsigned long long ) * EV_ECAP + sizeof( uint32_t ) * 2 * ( (size_t)bitwords + 1 );
+	return sizeof( rc_edge_t ) * (size_t)ecap + sizeof( unsigned long long ) * (size_t)ecap + sizeof( uint32_t ) * 2 * ( (size_t)bitwords + 1 );
 }
 
 __global__ void __launch_bounds__( EV_THREADS ) k_events( rc_work_t w )
@@ -46,9 +48,10 @@ __global__ void __launch_bounds__( EV_THREADS ) k_events( rc_work_t w )
 	extern __shared__ __align__( 16 ) unsigned char ev_smem[];
 	__shared__ int32_t s_wcnt[EV_WARPS][SP_LINES];
 	__shared__ int32_t s_warp[EV_WARPS];
+	__shared__ int32_t s_ne;
 	rc_edge_t *s_edge = reinterpret_cast<rc_edge_t *>( ev_smem );
-	unsigned long long *s_key = reinterpret_cast<unsigned long long *>( ev_smem + sizeof( rc_edge_t ) * EV_ECAP );
-	uint32_t *s_bm = reinterpret_cast<uint32_t *>( ev_smem + ( sizeof( rc_edge_t ) + sizeof( unsigned long long )) * EV_ECAP );
+	unsigned long long *s_key = reinterpret_cast<unsigned long long *>( ev_smem + sizeof( rc_edge_t ) * (size_t)w.ev_ecap );
+	uint32_t *s_bm = reinterpret_cast<uint32_t *>( ev_smem + ( sizeof( rc_edge_t ) + sizeof( unsigned long long )) * (size_t)w.ev_ecap );
 
 	const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
 	const int band = blockIdx.x, view = blockIdx.y, nbands = gridDim.x;
@@ -57,38 +60,63 @@ __global__ void __launch_bounds__( EV_THREADS ) k_events( rc_work_t w )
 	const int32_t y = band * SP_LINES + lane;
 	const bool valid = y >= y0 && y < y0 + vw_h && y < w.height;
 
-	int32_t ne = w.bandcnt[view * nbands + band];
-	if( ne > w.band_cap ) ne = w.band_cap;
-	const rc_edge_t *gedges = w.bandedges + ((size_t)view * nbands + band ) * w.band_cap;
+	const int32_t nview = min( w.nedges[view], w.max_edges );
+	const rc_edge_t *vedges = w.edges + (size_t)view * w.max_edges;
 	unsigned long long *arena = w.events + ((size_t)view * nbands + band ) * w.blk_events;
 	const int32_t bmwords = ( w.ncands[view] + 32 ) >> 5; /* surface numbers are candidate index + 1 */
 	uint32_t *s_pre = s_bm + bmwords;
 
-	/* A. stage the band's edges, mark the surfaces they belong to, sort keys = u at the band's middle line
-	 * (taken at the nearest line the edge is active on) */
-	const bool staged = ne <= EV_ECAP;
-	const rc_edge_t *E = staged ? s_edge : gedges;
+	/* A. gather the view's edges that cross this band (a view has a few hundred edges: every band block reads them
+	 * all, which is cheaper than k_faces scattering them into band lists with atomics), mark the surfaces they belong
+	 * to, sort keys = u at the band's middle line (taken at the nearest line the edge is active on) */
+	const int32_t yb0 = band * SP_LINES, yb1 = yb0 + SP_LINES - 1;
+	if( t == 0 ) s_ne = 0;
 	for( int32_t i = t; i < bmwords; i += EV_THREADS ) s_bm[i] = 0;
 	__syncthreads();
+	for( int32_t base = 0; base < nview; base += EV_THREADS )
+	{
+		const int32_t k = base + t;
+		rc_edge_t e;
+		bool in = false;
+		if( k < nview )
+		{
+			e = vedges[k];
+			const int32_t v = (int32_t)( e.vv & 0xFFFF ), v2 = (int32_t)( e.vv >> 16 );
+			in = v <= v2 && v <= yb1 && v2 >= yb0; /* reservations a face did not use have v > v2 */
+		}
+		const uint32_t m = __ballot_sync( 0xFFFFFFFFu, in );
+		int32_t wb = 0;
+		if( lane == 0 && m ) wb = atomicAdd( &s_ne, __popc( m ));
+		wb = __shfl_sync( 0xFFFFFFFFu, wb, 0 );
+		if( in )
+		{
+			const int32_t slot = wb + __popc( m & (( 1u << lane ) - 1u ));
+			if( slot < w.ev_ecap ) s_edge[slot] = e;
+			const int32_t s = (int32_t)(( e.surfs & 0xFFFF ) ? ( e.surfs & 0xFFFF ) : ( e.surfs >> 16 ));
+			atomicOr( &s_bm[s >> 5], 1u << ( s & 31 ));
+		}
+	}
+	__syncthreads();
+	/* more edges than the staging area holds: the lines read the view's edge list from HBM, unsorted */
+	const bool staged = s_ne <= w.ev_ecap;
+	if( t == 0 && !staged ) atomicAdd( &w.counters[RC_CTR_UNSTAGED_BANDS], 1ull );
+	const int32_t ne = staged ? s_ne : nview;
+	const rc_edge_t *E = staged ? s_edge : vedges;
 	int32_t npow = 32;
 	while( npow < ne ) npow <<= 1;
 	const int32_t ymid = band * SP_LINES + SP_LINES / 2;
-	for( int32_t k = t; k < ( staged ? npow : ne ); k += EV_THREADS )
-	{
-		if( k >= ne ) { s_key[k] = ~0ull; continue; }
-		const rc_edge_t e = gedges[k];
-		const int32_t s = (int32_t)(( e.surfs & 0xFFFF ) ? ( e.surfs & 0xFFFF ) : ( e.surfs >> 16 ));
-		atomicOr( &s_bm[s >> 5], 1u << ( s & 31 ));
-		if( staged )
+	if( staged )
+		for( int32_t k = t; k < npow; k += EV_THREADS )
 		{
-			s_edge[k] = e;
+			if( k >= ne ) { s_key[k] = ~0ull; continue; }
+			const rc_edge_t e = s_edge[k];
+			const int32_t s = (int32_t)(( e.surfs & 0xFFFF ) ? ( e.surfs & 0xFFFF ) : ( e.surfs >> 16 ));
 			const int32_t v = (int32_t)( e.vv & 0xFFFF ), v2 = (int32_t)( e.vv >> 16 );
 			const int32_t ym = ymid < v ? v : ( ymid > v2 ? v2 : ymid );
 			const uint32_t um = (uint32_t)e.u + (uint32_t)( ym - v ) * (uint32_t)e.u_step;
 			/* ties (the two copies of a shared edge) in the order the event keys will have: leading first, then by surface */
-			s_key[k] = ((unsigned long long)( um ^ 0x80000000u ) << 32 ) | (( e.surfs & 0xFFFF ) ? 1u << 27 : 0u ) | ((uint32_t)s << 11 ) | (uint32_t)k;
+			s_key[k] = ((unsigned long long)( um ^ 0x80000000u ) << 32 ) | (( e.surfs & 0xFFFF ) ? 1u << 29 : 0u ) | ((uint32_t)s << 13 ) | (uint32_t)k;
 		}
-	}
 	__syncthreads();
 
 	/* B. block bitonic sort of the keys: the order the lines will (nearly) need */
@@ -126,7 +154,7 @@ __global__ void __launch_bounds__( EV_THREADS ) k_events( rc_work_t w )
 		__syncthreads();
 	}
 	const int32_t nlocal = carry;
-	uint16_t *bsurf = w.bandsurf + ((size_t)view * nbands + band ) * ( (size_t)w.band_cap + 2 );
+	uint16_t *bsurf = w.bandsurf + ((size_t)view * nbands + band ) * ( (size_t)w.max_cands + 2 );
 	for( int32_t i = t; i < bmwords; i += EV_THREADS )
 	{
 		uint32_t m = s_bm[i];
@@ -149,7 +177,7 @@ __global__ void __launch_bounds__( EV_THREADS ) k_events( rc_work_t w )
 	int32_t cnt = 0;
 	for( int32_t k = k0; k < k1; k++ )
 	{
-		const uint32_t vv = E[staged ? (int32_t)( (uint32_t)s_key[k] & 2047u ) : k].vv;
+		const uint32_t vv = E[staged ? (int32_t)( (uint32_t)s_key[k] & 8191u ) : k].vv;
 		cnt += ( valid && y >= (int32_t)( vv & 0xFFFF ) && y <= (int32_t)( vv >> 16 )) ? 1 : 0;
 	}
 	s_wcnt[warp][lane] = cnt;
@@ -186,7 +214,7 @@ __global__ void __launch_bounds__( EV_THREADS ) k_events( rc_work_t w )
 	int32_t pos = off + mybase;
 	for( int32_t k = k0; k < k1; k++ )
 	{
-		const rc_edge_t e = E[staged ? (int32_t)( (uint32_t)s_key[k] & 2047u ) : k];
+		const rc_edge_t e = E[staged ? (int32_t)( (uint32_t)s_key[k] & 8191u ) : k];
 		const int32_t v = (int32_t)( e.vv & 0xFFFF );
 		if( y >= v && y <= (int32_t)( e.vv >> 16 ))
 		{
@@ -340,15 +368,17 @@ __global__ void __launch_bounds__( LN_WARPS * 32, 8 ) k_lines( rc_work_t w )
 	/* scanlines differ a lot in cost (2 .. 500 events) and the heavy ones cluster (the horizon of corridor views):
 	 * warps draw them from a shared cursor, view-interleaved */
 	/* two sweeps over the lines: the heavy ones first (longest processing time first keeps the tail short) */
+	/* lines per cursor grab: LN_CHUNK when every warp gets many lines, one when lines are few and long (big frames) */
+	const int32_t chunk = nlines >= (int32_t)gridDim.x * LN_WARPS * 8 ? LN_CHUNK : 1;
 	for( int32_t q = 0, heavy = 1; ; q++ )
 	{
 		int32_t item = 0;
-		if(( q & ( LN_CHUNK - 1 )) == 0 )
+		if(( q & ( chunk - 1 )) == 0 )
 		{
-			if( lane == 0 ) item = atomicAdd( w.line_cursor + ( heavy ? 0 : 1 ), LN_CHUNK );
+			if( lane == 0 ) item = atomicAdd( w.line_cursor + ( heavy ? 0 : 1 ), chunk );
 			cur = __shfl_sync( 0xFFFFFFFFu, item, 0 );
 		}
-		item = cur + ( q & ( LN_CHUNK - 1 ));
+		item = cur + ( q & ( chunk - 1 ));
 		if( cur >= nlines )
 		{
 			if( !heavy )
@@ -458,7 +488,7 @@ __global__ void __launch_bounds__( LN_WARPS * 32, 8 ) k_lines( rc_work_t w )
 		const long long dbg1 = clock64();
 #endif
 		const int32_t bandix = view * w.nbands + ( line - view * w.height ) / SP_LINES;
-		const uint16_t *bsurf = w.bandsurf + (size_t)bandix * ( (size_t)w.band_cap + 2 );
+		const uint16_t *bsurf = w.bandsurf + (size_t)bandix * ( (size_t)w.max_cands + 2 );
 		const int32_t nwords = ( w.bandnloc[bandix] + 32 ) >> 5; /* band-local surface numbers */
 		uint32_t *bits = s_bits[warp];
 		if( nwords > SP_BITWORDS )

@@ -35,7 +35,7 @@ class RefViewpass(C.Structure):
 assert C.sizeof(RefViewpass) == 56
 
 CTR_NAMES = ["views", "pixels", "cands", "surfs", "edges", "spans", "cache_blocks", "cache_texels",
-             "overflow_edges", "overflow_events", "overflow_stack", "overflow_cands", "serial_lines", "sorted_lines"]
+             "overflow_edges", "overflow_events", "overflow_stack", "overflow_cands", "serial_lines", "sorted_lines", "unstaged_bands"]
 
 
 @functools.lru_cache(maxsize=8)
