@@ -525,8 +525,9 @@ int launch_slice( const rc_work_t &ws, cudaStream_t st, cudaEvent_t *evs, bool d
 	if( evs ) CK( cudaEventRecord( evs[4], st ));
 	if( draw )
 	{
-		const int dblocks = ( nlines + DR_WARPS - 1 ) / DR_WARPS;
-		k_draw<<<dblocks < DR_GRID ? dblocks : DR_GRID, DR_WARPS * 32, rc_draw_smem( ws.width ), st>>>( sc, ws, 0, nlines );
+		const int lpw = rc_draw_lpw( ws.width, ws.height );
+		const int dblocks = ( nlines / lpw + DR_WARPS - 1 ) / DR_WARPS;
+		k_draw<<<dblocks < DR_GRID ? dblocks : DR_GRID, DR_WARPS * 32, rc_draw_smem( ws.width, lpw ), st>>>( sc, ws, 0, nlines, lpw );
 		D.launches++;
 	}
 	if( evs ) CK( cudaEventRecord( evs[5], st ));
@@ -602,7 +603,7 @@ int rc_dev_init( int device )
 	for( auto &e : D.ev ) CK( cudaEventCreate( &e ));
 	CK( cudaFuncSetAttribute( k_viswalk<VW_NTHREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 64 ));
 	CK( cudaFuncSetAttribute( k_events, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_events_smem( EV_ECAP_MAX, 65536 / 32 + 2 )));
-	CK( cudaFuncSetAttribute( k_draw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_draw_smem( 8192 )));
+	CK( cudaFuncSetAttribute( k_draw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_draw_smem( 8192, 1 )));
 	for( int i = 0; i < 256; i++ ) D.h_styles[i] = 256;
 	if( upload( &D.d_styles, D.h_styles, 256 ) != 0 ) return -1;
 	if( dalloc( &D.d_counters, RC_CTR_COUNT ) != 0 ) return -1;
