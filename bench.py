@@ -304,6 +304,17 @@ def run_cuda(args):
     ms_cache = allmax(st_rb[2])
     cache_texels = r.counters()["cache_texels"]
 
+    # -- display tail: the batch's frames, resident in HBM, converted to XRGB8888 by k_blit
+    #    (2 B read + 4 B written per pixel), outside the headline timing; kernel time from CUDA events in the plugin
+    import ctypes as _C
+    blit_ms = []
+    _ms = _C.c_float()
+    for _ in range(max(args.warmup, 3) + max(3, args.steps // 4)):
+        if r._blit(0, n, None, w, 4, 0x00FF0000, 0x0000FF00, 0x000000FF, _C.byref(_ms)) != 0:
+            raise SystemExit("bench.py: RefCuda_BlitViews failed")
+        blit_ms.append(_ms.value)
+    ms_blit = allmax(float(np.median(blit_ms[max(args.warmup, 3):])))
+
     # -- e2e: the public C-ABI call with host buffers (H2D view descriptors, D2H colour frames), wall clock
     for _ in range(max(args.warmup, 3)):
         r.render_prepared(vp, pin.data_ptr(), None)
@@ -343,6 +354,9 @@ def run_cuda(args):
                                        "peak": peak, "unit": "GB/s", "frac": 4 * cache_texels / (ms_cache * 1e-3) / 1e9 / peak,
                                        "algorithmic_bytes_per_launch": 4 * cache_texels, "kernel_ms": ms_cache, "traffic": measured_traffic("k_cache_build_dram_bytes_per_launch"),
                                        "note": "forced rebuild of every (face, mip) block this rank's batch samples: 4 B per cache texel (2 B texel read + 2 B written), luxel bytes not counted"},
+            "roofline_display_tail": {"bound": "hbm", "kernel": "k_blit<4> (pixel_t -> XRGB8888)", "achieved": 6 * px / (ms_blit * 1e-3) / 1e9, "peak": peak,
+                                      "unit": "GB/s", "frac": 6 * px / (ms_blit * 1e-3) / 1e9 / peak, "algorithmic_bytes_per_launch": 6 * px,
+                                      "kernel_ms": ms_blit, "traffic": None, "note": "2 B pixel_t read + 4 B display pixel written; 256 KB screen map in L2; not part of value / e2e"},
             "clocks": clocks, "counters": counters, "device": r.device_name(),
         }
         if world == 1 and not args.no_cpu_baseline:

@@ -39,6 +39,16 @@ REF_CUDA_EXPORT int GetRefAPI( int version, struct ref_interface_s *pFunctionTab
  */
 REF_CUDA_EXPORT int RefCuda_RenderViews( const struct ref_viewpass_s *views, int nviews, unsigned short *color_out, short *z_out, int clear );
 
+/*
+ * Display tail on the device (R_BuildScreenMap + R_BlitScreen, ref/soft/r_glblit.c:347-407,591-721): converts views
+ * [first, first + nviews) of the last RefCuda_RenderViews batch, which stay in HBM, from pixel_t to a display format
+ * described the way SW_CreateBuffer (engine/ref_api.h) describes the engine's surface - bpp 2 or 4 bytes and the three
+ * channel masks - and writes them to dst[nviews * height][stride] (stride in pixels, >= width).  dst NULL: conversion
+ * only.  ms_kernel (optional): CUDA-event milliseconds of the conversion kernel.  Returns 0 on success.
+ */
+REF_CUDA_EXPORT int RefCuda_BlitViews( int first, int nviews, void *dst, unsigned int stride, unsigned int bpp,
+	unsigned int rmask, unsigned int gmask, unsigned int bmask, float *ms_kernel );
+
 /* Re-run the device stages of the last batch with all inputs resident in HBM; CUDA-event milliseconds
  * per iteration: total and per stage, ms_stage[5] = [visibility+BSP walk, face/edge set-up, surface cache,
  * span generation, span drawing].

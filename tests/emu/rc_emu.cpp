@@ -263,6 +263,10 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 	return 0;
 }
 
+/* the display tail is not part of the debug harness (it keeps no frames) */
+int rc_dev_set_screenmap( const uint32_t *, int ) { return 0; }
+int rc_dev_blit( int, int, void *, size_t, float * ) { snprintf( E.err, sizeof( E.err ), "display tail: not in the debug harness" ); return -1; }
+
 int rc_dev_bench_resident( int, int, float *ms_total, float *ms_stage )
 {
 	if( ms_total ) *ms_total = 0;

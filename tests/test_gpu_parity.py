@@ -6,6 +6,7 @@ Bars (BASELINE.json north_star): surface-cache blocks bit-exact; framebuffer and
 pixels with every residual pixel within 1 px of a surface boundary of the reference image.
 """
 import hashlib
+import importlib
 
 import numpy as np
 import pytest
@@ -250,3 +251,48 @@ def test_c3_mechanism_medium_map_1080p(pkg, scene):
                     assert np.array_equal(a, b), (step, s, mip)
                     n += 1
         assert n > 0
+
+
+DISPLAY_FORMATS = [(2, 0xF800, 0x07E0, 0x001F), (4, 0x00FF0000, 0x0000FF00, 0x000000FF)]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("fmt", DISPLAY_FORMATS)
+def test_display_tail_matches_reference_blit(pkg, scene, fmt):
+    """RefCuda_BlitViews (k_blit over the frames resident in HBM) against what the unmodified
+    R_EndFrame / R_BlitScreen leaves in the software surface; bit-exact."""
+    m = scene.make_map("small", ncameras=32)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m, sw_format=fmt)
+    cu = scene.Renderer(pkg.REF_CUDA_PATH, 320, 240, m, sw_format=fmt)
+    want = so.blit_views(m.cameras[:12])
+    got = cu.blit_views(m.cameras[:12])
+    assert got.dtype == want.dtype and np.array_equal(got, want)
+    # a second format on the same renderer: the screen map is rebuilt
+    other = DISPLAY_FORMATS[1] if fmt == DISPLAY_FORMATS[0] else DISPLAY_FORMATS[0]
+    hostlib = importlib.import_module("xash3d-fwgs_b200.hostlib")
+    col, _ = so.render_views(m.cameras[:12])
+    got2 = cu.blit_views(m.cameras[:12], sw_format=other)
+    assert np.array_equal(got2.astype(np.uint32), hostlib.screen_map(other)[col])
+
+
+@pytest.mark.gpu
+def test_stock_frame_loop_fills_the_software_surface(pkg, scene):
+    """The path the engine drives - R_BeginFrame, GL_RenderFrame, R_EndFrame, one view per frame - leaves the same
+    display pixels in the SW_LockBuffer surface as ref_soft does."""
+    m = scene.make_map("small", ncameras=16)
+    fmt = DISPLAY_FORMATS[1]
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m, sw_format=fmt)
+    cu = scene.Renderer(pkg.REF_CUDA_PATH, 320, 240, m, sw_format=fmt)
+    l0 = cu.launch_count()
+    got = cu.frame_views(m.cameras[:3])
+    assert cu.launch_count() > l0
+    assert np.array_equal(got, so.blit_views(m.cameras[:3]))
+
+
+@pytest.mark.gpu
+def test_display_tail_ragged_frame_size(pkg, scene):
+    """A frame whose pixel count is not a multiple of 8 (the vector width of k_blit and of the row stores)."""
+    m = scene.make_map("tiny", ncameras=16)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 322, 241, m)
+    cu = scene.Renderer(pkg.REF_CUDA_PATH, 322, 241, m)
+    assert np.array_equal(cu.blit_views(m.cameras[:5]), so.blit_views(m.cameras[:5]))

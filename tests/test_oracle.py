@@ -76,3 +76,19 @@ def test_stage_functions_match_oracle_on_cpu(pkg, scene, which, n, wh):
                 assert np.array_equal(a, b), (s, mip)
                 checked += 1
     assert checked > 0
+
+
+@pytest.mark.parametrize("fmt", [(2, 0xF800, 0x07E0, 0x001F), (4, 0x00FF0000, 0x0000FF00, 0x000000FF), (4, 0x000000FF, 0x0000FF00, 0x00FF0000)])
+def test_screen_map_restatement_matches_reference_blit(pkg, scene, fmt):
+    """Display tail: what the unmodified R_EndFrame / R_BlitScreen writes to the software surface is the
+    pixel_t frame looked up in the screen map; pins hostlib.screen_map (R_BuildScreenMap restated) for RGB565,
+    XRGB8888 and XBGR8888 surfaces."""
+    hostlib = __import__("importlib").import_module("xash3d-fwgs_b200.hostlib")
+    m = scene.make_map("tiny", ncameras=16)
+    r = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m, sw_format=fmt)
+    col, _ = r.render_views(m.cameras[:4])
+    disp = r.blit_views(m.cameras[:4])
+    table = hostlib.screen_map(fmt)
+    assert disp.dtype == (np.uint16 if fmt[0] == 2 else np.uint32)
+    assert np.array_equal(disp.astype(np.uint32), table[col])
+    assert len(np.unique(disp)) > 16

@@ -227,13 +227,29 @@ static intptr_t xh_EngineGetParm( int parm, int arg )
 /* software "window": the engine hands out an RGB565 surface (engine/platform/sdl2/vid_sdl2.c:52-229) */
 static qboolean xh_SW_CreateBuffer( int w, int h, uint *stride, uint *bpp, uint *r, uint *g, uint *b )
 {
+	if( !xh.sw_bpp ) { xh.sw_bpp = 2; xh.sw_mask[0] = 0xF800; xh.sw_mask[1] = 0x07E0; xh.sw_mask[2] = 0x001F; }
 	free( xh.swbuffer );
-	xh.swbuffer = calloc((size_t)w * h, 2 );
+	xh.swbuffer = calloc((size_t)w * h, xh.sw_bpp );
 	xh.sw_w = w; xh.sw_h = h;
-	*stride = w; *bpp = 2; *r = 0xF800; *g = 0x07E0; *b = 0x001F;
+	*stride = w; *bpp = xh.sw_bpp; *r = xh.sw_mask[0]; *g = xh.sw_mask[1]; *b = xh.sw_mask[2];
 	return xh.swbuffer != NULL;
 }
 static void *xh_SW_LockBuffer( void ) { return xh.swbuffer; }
+
+/* display format of the software surface handed to the renderer; call before xh_init (default RGB565) */
+void xh_set_sw_format( unsigned bpp, unsigned rmask, unsigned gmask, unsigned bmask )
+{
+	xh.sw_bpp = bpp; xh.sw_mask[0] = rmask; xh.sw_mask[1] = gmask; xh.sw_mask[2] = bmask;
+}
+
+/* the software surface (what R_EndFrame / R_BlitScreen wrote) */
+const void *xh_sw_buffer( int *w, int *h, int *bpp )
+{
+	if( w ) *w = xh.sw_w;
+	if( h ) *h = xh.sw_h;
+	if( bpp ) *bpp = (int)xh.sw_bpp;
+	return xh.swbuffer;
+}
 static void xh_SW_UnlockBuffer( void ) {}
 
 static void xh_R_StoreEfrags( struct efrag_s **pp, int framecount ) { (void)pp; (void)framecount; }
@@ -517,6 +533,24 @@ void xh_render_view( const float *origin, const float *angles, float fov_x, floa
 	rvp.flags = flags;
 	for( int i = 0; i < 3; i++ ) { xh.refState.vieworg[i] = origin[i]; xh.refState.viewangles[i] = angles[i]; }
 	xh.ref.GL_RenderFrame( &rvp );
+}
+
+/* the engine's frame loop for one view per frame: R_BeginFrame, GL_RenderFrame, R_EndFrame; the software surface
+ * (display format) is copied out after each frame.  Works with any renderer plugin. */
+int xh_frame_views( const float *cams, int n, float fov_x, float fov_y, int x, int y, int w, int h, int flags, void *display_out )
+{
+	for( int i = 0; i < n; i++ )
+	{
+		const float *c = cams + 6 * i;
+		xh.ref.R_BeginFrame( false );
+		xh_render_view( c, c + 3, fov_x, fov_y, x, y, w, h, flags );
+		xh.ref.R_EndFrame();
+		if( !xh.swbuffer )
+			return -1;
+		size_t bytes = (size_t)xh.sw_w * xh.sw_h * xh.sw_bpp;
+		memcpy((char *)display_out + bytes * i, xh.swbuffer, bytes );
+	}
+	return 0;
 }
 
 void xh_clear_scene( void ) { xh.ref.R_ClearScene(); }

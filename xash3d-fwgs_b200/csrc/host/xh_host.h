@@ -69,6 +69,14 @@ XH_EXPORT const void *xh_soft_cache_block( int surf, int mip, int *width, int *h
  * per view; returns the seconds spent inside GL_RenderFrame (xh_probe_soft.c) */
 XH_EXPORT double xh_soft_render_views( const float *cams, int n, float fov_x, float fov_y, int x, int y, int w, int h, int flags, int clear,
 	unsigned short *color_out, short *z_out );
+/* display format of the software surface handed out by SW_CreateBuffer (call before xh_init; default RGB565), and the
+ * surface itself (what R_EndFrame wrote) */
+XH_EXPORT void xh_set_sw_format( unsigned bpp, unsigned rmask, unsigned gmask, unsigned bmask );
+XH_EXPORT const void *xh_sw_buffer( int *w, int *h, int *bpp );
+/* the engine's frame loop, one view per frame (R_BeginFrame, GL_RenderFrame, R_EndFrame), any renderer plugin */
+XH_EXPORT int xh_frame_views( const float *cams, int n, float fov_x, float fov_y, int x, int y, int w, int h, int flags, void *display_out );
+/* oracle-only: the views one by one through GL_RenderFrame + R_EndFrame (R_BlitScreen); surface copied out per view */
+XH_EXPORT int xh_soft_blit_views( const float *cams, int n, float fov_x, float fov_y, int x, int y, int w, int h, int flags, void *display_out );
 
 #ifdef __cplusplus
 }

@@ -52,6 +52,7 @@ typedef struct
 
 	void            *swbuffer;
 	int             sw_w, sw_h;
+	unsigned        sw_bpp, sw_mask[3];
 
 	/* world */
 	model_t         *world;

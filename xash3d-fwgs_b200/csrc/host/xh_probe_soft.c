@@ -64,3 +64,34 @@ double xh_soft_render_views( const float *cams, int n, float fov_x, float fov_y,
 	}
 	return total;
 }
+
+/*
+ * ORACLE-ONLY: the display tail of the reference.  Renders the views one after another like xh_soft_render_views and
+ * ends the frame after each (R_EndFrame -> R_BlitScreen, ref/soft/r_main.c:1182, r_glblit.c:591), copying the
+ * software surface (format: xh_set_sw_format) to display_out[n][h][w].
+ */
+int xh_soft_blit_views( const float *cams, int n, float fov_x, float fov_y, int x, int y, int w, int h, int flags, void *display_out )
+{
+	viddef_t *pvid = (viddef_t *)xh_ref_symbol( "vid" );
+	short **pz = (short **)xh_ref_symbol( "d_pzbuffer" );
+	int *oldcluster = (int *)xh_ref_symbol( "r_oldviewcluster" );
+	int sw_w, sw_h, bpp;
+	if( !pvid || !pz || !oldcluster )
+		return -1;
+	size_t px = (size_t)pvid->width * pvid->height;
+	for( int i = 0; i < n; i++ )
+	{
+		const float *c = cams + 6 * i;
+		memset( pvid->buffer, 0, px * sizeof( pixel_t ));
+		memset( *pz, 0, px * sizeof( short ));
+		*oldcluster = -2;
+		xh_begin_frame();
+		xh_render_view( c, c + 3, fov_x, fov_y, x, y, w, h, flags );
+		xh_end_frame();
+		const void *sw = xh_sw_buffer( &sw_w, &sw_h, &bpp );
+		if( !sw || (size_t)sw_w * sw_h != px )
+			return -2;
+		memcpy((char *)display_out + px * bpp * i, sw, px * bpp );
+	}
+	return 0;
+}

@@ -47,6 +47,13 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 #define RC_BENCH_STAGES        5 /* vis+walk, faces, cache, spans, draw */
 int rc_dev_bench_resident( int iters, int flags, float *ms_total, float *ms_stage /* [RC_BENCH_STAGES] */ );
 
+/* display tail (R_BuildScreenMap / R_BlitScreen, ref/soft/r_glblit.c:347,591): table[65536] maps pixel_t to the
+ * display format (bpp 2: low 16 bits used; bpp 4).  rc_dev_blit converts views [first, first + nviews) of the last
+ * batch, resident in HBM, and copies them to dst[nviews * height][stride] (pixels; NULL: conversion only);
+ * ms_kernel (optional): CUDA-event time of the conversion kernel */
+int rc_dev_set_screenmap( const uint32_t *table, int bpp );
+int rc_dev_blit( int first, int nviews, void *dst, size_t stride, float *ms_kernel );
+
 /* probes for the parity tests */
 int rc_dev_read_cache_block( int surf, int mip, uint16_t *out, int maxtexels, int *width, int *height, int *valid );
 int rc_dev_read_counters( uint64_t *out, int n );

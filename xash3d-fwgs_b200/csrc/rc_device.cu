@@ -326,6 +326,44 @@ __global__ void __launch_bounds__( CACHE_THREADS ) k_cache_build( rc_scene_t sc,
 
 namespace {
 
+/* ---------------------------------------------------------------------------------------------- */
+/* display tail: R_BlitScreen (ref/soft/r_glblit.c:591-721) - every pixel_t goes through the 65536-entry
+ * screen map (vid.screen / vid.screen32, built like R_BuildScreenMap by the host side).  HBM bound:
+ * 2 B read + bpp B written per pixel; the table (256 KB) lives in L2.  Thread = 8 pixels.            */
+
+template <int BPP>
+__global__ void __launch_bounds__( 256 ) k_blit( const uint16_t *__restrict__ color, const uint32_t *__restrict__ lut, void *out, size_t npx )
+{
+	const size_t n8 = npx >> 3;
+	for( size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x )
+	{
+		const uint4 in = __ldg( reinterpret_cast<const uint4 *>( color ) + i );
+		const uint32_t p[4] = { in.x, in.y, in.z, in.w };
+		uint32_t o[8];
+#pragma unroll
+		for( int k = 0; k < 4; k++ )
+		{
+			o[2 * k] = __ldg( lut + ( p[k] & 0xFFFFu ));
+			o[2 * k + 1] = __ldg( lut + ( p[k] >> 16 ));
+		}
+		if( BPP == 2 )
+			reinterpret_cast<uint4 *>( out )[i] = make_uint4( o[0] | ( o[1] << 16 ), o[2] | ( o[3] << 16 ), o[4] | ( o[5] << 16 ), o[6] | ( o[7] << 16 ));
+		else
+		{
+			reinterpret_cast<uint4 *>( out )[2 * i] = make_uint4( o[0], o[1], o[2], o[3] );
+			reinterpret_cast<uint4 *>( out )[2 * i + 1] = make_uint4( o[4], o[5], o[6], o[7] );
+		}
+	}
+	/* ragged tail (frame sizes that are not a multiple of 8 pixels) */
+	if( blockIdx.x == 0 )
+		for( size_t x = ( n8 << 3 ) + threadIdx.x; x < npx; x += blockDim.x )
+		{
+			const uint32_t v = __ldg( lut + color[x] );
+			if( BPP == 2 ) reinterpret_cast<uint16_t *>( out )[x] = (uint16_t)v;
+			else reinterpret_cast<uint32_t *>( out )[x] = v;
+		}
+}
+
 struct Dev
 {
 	bool ready = false;
@@ -364,6 +402,12 @@ struct Dev
 	void *d_work[20] = {};
 	bool have_batch = false;
 	void *d_flush = nullptr;
+
+	/* display tail */
+	uint32_t *d_screenmap = nullptr;
+	int screen_bpp = 0;
+	void *d_display = nullptr;
+	size_t display_bytes = 0;
 } D;
 
 bool ck( cudaError_t e, const char *what )
@@ -618,6 +662,8 @@ void rc_dev_shutdown( void )
 	if( !D.ready ) return;
 	cudaDeviceSynchronize();
 	free_batch();
+	if( D.d_display ) { cudaFree( D.d_display ); D.d_display = nullptr; D.display_bytes = 0; }
+	if( D.d_screenmap ) { cudaFree( D.d_screenmap ); D.d_screenmap = nullptr; }
 	D.ready = false;
 }
 
@@ -835,6 +881,51 @@ int rc_dev_read_cache_block( int surf, int mip, uint16_t *out, int maxtexels, in
 	*valid = !stale;
 	if( *valid && bw * bh <= maxtexels )
 		CK( cudaMemcpy( out, D.sc.cache + sf->cache_ofs[mip], (size_t)bw * bh * 2, cudaMemcpyDeviceToHost ));
+	return 0;
+}
+
+int rc_dev_set_screenmap( const uint32_t *table, int bpp )
+{
+	if( bpp != 2 && bpp != 4 ) { snprintf( D.err, sizeof( D.err ), "rc_dev_set_screenmap: bpp %d not supported (2 or 4)", bpp ); return -1; }
+	if( !D.d_screenmap && dalloc( &D.d_screenmap, 65536 ) != 0 ) return -1;
+	CK( cudaMemcpy( D.d_screenmap, table, sizeof( uint32_t ) * 65536, cudaMemcpyHostToDevice ));
+	D.screen_bpp = bpp;
+	return 0;
+}
+
+int rc_dev_blit( int first, int nviews, void *dst, size_t stride, float *ms_kernel )
+{
+	if( !D.have_batch || !D.d_screenmap || first < 0 || nviews < 0 || first + nviews > D.w.nviews )
+	{
+		snprintf( D.err, sizeof( D.err ), "rc_dev_blit: no batch / no screen map / views out of range" );
+		return -1;
+	}
+	const size_t fpx = (size_t)D.w.width * D.w.height, npx = fpx * nviews, bytes = npx * D.screen_bpp;
+	if( !npx ) return 0;
+	if( bytes > D.display_bytes )
+	{
+		if( D.d_display ) cudaFree( D.d_display );
+		D.d_display = nullptr; D.display_bytes = 0;
+		CK( cudaMalloc( &D.d_display, bytes ));
+		D.display_bytes = bytes;
+	}
+	const uint16_t *src = D.w.color + fpx * first;
+	const size_t want = ( npx / 8 + 255 ) / 256;
+	const int grid = (int)( want < 148 * 8 ? ( want ? want : 1 ) : 148 * 8 );
+	if( ms_kernel ) CK( cudaEventRecord( D.ev[6], D.stream ));
+	if( D.screen_bpp == 2 ) k_blit<2><<<grid, 256, 0, D.stream>>>( src, D.d_screenmap, D.d_display, npx );
+	else k_blit<4><<<grid, 256, 0, D.stream>>>( src, D.d_screenmap, D.d_display, npx );
+	D.launches++;
+	if( ms_kernel ) CK( cudaEventRecord( D.ev[7], D.stream ));
+	CK( cudaGetLastError());
+	if( dst )
+	{
+		const size_t rowbytes = (size_t)D.w.width * D.screen_bpp;
+		if( stride < (size_t)D.w.width ) { snprintf( D.err, sizeof( D.err ), "rc_dev_blit: stride smaller than the frame width" ); return -1; }
+		CK( cudaMemcpy2DAsync( dst, stride * D.screen_bpp, D.d_display, rowbytes, rowbytes, (size_t)D.w.height * nviews, cudaMemcpyDeviceToHost, D.stream ));
+	}
+	CK( cudaStreamSynchronize( D.stream ));
+	if( ms_kernel ) CK( cudaEventElapsedTime( ms_kernel, D.ev[6], D.ev[7] ));
 	return 0;
 }
 

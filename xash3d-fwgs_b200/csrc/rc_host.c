@@ -88,12 +88,10 @@ static struct
 	/* view queue between R_BeginFrame and R_EndFrame */
 	rc_view_t   *views;
 	int          nviews, maxviews;
-	uint16_t    *framebuf; /* host copy of the last flushed batch's first view (blit source) */
-	int16_t     *zbuf;
-	int          fb_w, fb_h;
 
 	void        *swbuffer_info_valid;
 	uint         sw_stride, sw_bpp, sw_r, sw_g, sw_b;
+	uint         map_valid, map_bpp, map_r, map_g, map_b; /* display format the device's screen map was built for */
 	char         error[512];
 } rc;
 
@@ -780,17 +778,6 @@ static void rc_queue_view( const ref_viewpass_t *rvp )
 	rc_setup_view( rvp, &rc.views[rc.nviews++] );
 }
 
-static void rc_ensure_framebuf( void )
-{
-	int w = gpGlobals->width, h = gpGlobals->height;
-	if( rc.framebuf && rc.fb_w == w && rc.fb_h == h )
-		return;
-	rc_free( rc.framebuf ); rc_free( rc.zbuf );
-	rc.framebuf = rc_malloc((size_t)w * h * 2 );
-	rc.zbuf = rc_malloc((size_t)w * h * 2 );
-	rc.fb_w = w; rc.fb_h = h;
-}
-
 static void R_BeginFrame( qboolean clearScene ) { (void)clearScene; rc.nviews = 0; }
 
 /* GL_RenderFrame slot == R_RenderFrame (ref/soft/r_main.c:1141): here the view is only recorded */
@@ -803,31 +790,74 @@ static void R_RenderFrame( const ref_viewpass_t *rvp )
 
 static void R_RenderScene( void ) {}
 
-/* pixel_t -> display format of the engine's software surface (R_BuildScreenMap + R_BlitScreen,
- * ref/soft/r_glblit.c:347-407,591-721) for the first queued view */
+/* pixel_t -> display format of the engine's software surface.  The table is R_BuildScreenMap's
+ * (ref/soft/r_glblit.c:347-407): entry (i << 8 | j) = major(i) | minor(j), every 5/6/5-bit channel value c
+ * rescaled as c * 2^bits / (31 | 63 | 31) and shifted to its mask.  The per-pixel lookup (R_BlitScreen,
+ * r_glblit.c:591-721) is k_blit on the device. */
 static uint rc_mask_shift( uint m ) { uint s = 0; if( !m ) return 0; while( !( m & 1 )) { m >>= 1; s++; } return s; }
 static uint rc_mask_bits( uint m ) { uint c = 0; while( m ) { c += m & 1; m >>= 1; } return c; }
+#define RC_BIT_TO( v, from, to ) (((( v ) >> ( from )) & 1u ) << ( to ))
+
+static void rc_build_screenmap( uint32_t *table, uint rmask, uint gmask, uint bmask )
+{
+	const uint rs = rc_mask_shift( rmask ), gs = rc_mask_shift( gmask ), bs = rc_mask_shift( bmask );
+	const uint rm = 1u << rc_mask_bits( rmask ), gm = 1u << rc_mask_bits( gmask ), bm = 1u << rc_mask_bits( bmask );
+	uint32_t major[256], minor[256];
+	for( uint i = 0; i < 256; i++ )
+	{
+		/* major byte: 3-3-2 bits of r, g, b at the top of the 5/6/5-bit channels */
+		uint r = (( i >> 5 ) << 2 ) & 31u, g = (( i >> 2 ) << 3 ) & 63u, b = ( i << 3 ) & 31u;
+		major[i] = ( r * rm / 31u ) << rs | ( g * gm / 63u ) << gs | ( b * bm / 31u ) << bs;
+		/* minor byte: the low channel bits, interleaved G B R G B R G B from bit 7 down */
+		r = RC_BIT_TO( i, 5, 1 ) | RC_BIT_TO( i, 2, 0 );
+		g = RC_BIT_TO( i, 7, 2 ) | RC_BIT_TO( i, 4, 1 ) | RC_BIT_TO( i, 1, 0 );
+		b = RC_BIT_TO( i, 6, 2 ) | RC_BIT_TO( i, 3, 1 ) | RC_BIT_TO( i, 0, 0 );
+		minor[i] = ( r * rm / 31u ) << rs | ( g * gm / 63u ) << gs | ( b * bm / 31u ) << bs;
+	}
+	for( uint i = 0; i < 256; i++ )
+		for( uint j = 0; j < 256; j++ )
+			table[( i << 8 ) | j] = major[i] | minor[j];
+}
+
+static int rc_set_display_format( uint bpp, uint rmask, uint gmask, uint bmask )
+{
+	if( rc.map_valid && rc.map_bpp == bpp && rc.map_r == rmask && rc.map_g == gmask && rc.map_b == bmask )
+		return 0;
+	uint32_t *table = rc_malloc( sizeof( uint32_t ) * 65536 );
+	rc_build_screenmap( table, rmask, gmask, bmask );
+	int rcode = rc_dev_set_screenmap( table, (int)bpp );
+	rc_free( table );
+	if( rcode )
+		return rcode;
+	rc.map_valid = 1; rc.map_bpp = bpp; rc.map_r = rmask; rc.map_g = gmask; rc.map_b = bmask;
+	return 0;
+}
 
 static void rc_blit_screen( void )
 {
 	void *dst = gEngfuncs.SW_LockBuffer();
 	if( !dst )
 		return;
-	uint rs = rc_mask_shift( rc.sw_r ), gs = rc_mask_shift( rc.sw_g ), bs = rc_mask_shift( rc.sw_b );
-	uint rm = 1u << rc_mask_bits( rc.sw_r ), gm = 1u << rc_mask_bits( rc.sw_g ), bm = 1u << rc_mask_bits( rc.sw_b );
-	int w = rc.fb_w, h = rc.fb_h;
-	for( int y = 0; y < h; y++ )
-		for( int x = 0; x < w; x++ )
+	RC_CHECK_DEV( rc_set_display_format( rc.sw_bpp, rc.sw_r, rc.sw_g, rc.sw_b ));
+	if( rc.nviews == 1 )
+	{
+		RC_CHECK_DEV( rc_dev_blit( 0, 1, dst, rc.sw_stride, NULL ));
+	}
+	else
+	{
+		/* several passes in one frame share the screen in the reference; composite their viewports */
+		const int w = gpGlobals->width, h = gpGlobals->height;
+		const size_t px = (size_t)w * h, bpp = rc.sw_bpp;
+		byte *all = rc_malloc( px * bpp * rc.nviews );
+		RC_CHECK_DEV( rc_dev_blit( 0, rc.nviews, all, w, NULL ));
+		for( int i = 0; i < rc.nviews; i++ )
 		{
-			uint r, g, b;
-			rc_decode565( rc.framebuf[y * w + x], &r, &g, &b );
-			/* major and minor parts are scaled separately and or-ed, as the reference's table does */
-			uint rM = r & ~3u, gM = g & ~7u, bM = b & ~7u;
-			uint px = (( rM * rm / 31 ) << rs | ( gM * gm / 63 ) << gs | ( bM * bm / 31 ) << bs )
-				| ((( r & 3 ) * rm / 31 ) << rs | (( g & 7 ) * gm / 63 ) << gs | (( b & 7 ) * bm / 31 ) << bs );
-			if( rc.sw_bpp == 2 ) ((uint16_t *)dst )[y * rc.sw_stride + x] = (uint16_t)px;
-			else ((uint32_t *)dst )[y * rc.sw_stride + x] = px;
+			const int *vr = rc.views[i].vrect;
+			for( int y = vr[1]; y < vr[1] + vr[3] && y < h; y++ )
+				memcpy((byte *)dst + ((size_t)y * rc.sw_stride + vr[0] ) * bpp, all + ( px * i + (size_t)y * w + vr[0] ) * bpp, (size_t)Q_min( vr[2], w - vr[0] ) * bpp );
 		}
+		rc_free( all );
+	}
 	gEngfuncs.SW_UnlockBuffer();
 }
 
@@ -837,25 +867,8 @@ static void R_EndFrame( void )
 	{
 		int w = gpGlobals->width, h = gpGlobals->height;
 		rc_prepare_batch();
-		rc_ensure_framebuf();
-		if( rc.nviews == 1 )
-		{
-			RC_CHECK_DEV( rc_dev_render( rc.views, 1, w, h, 0, rc.framebuf, rc.zbuf ));
-		}
-		else
-		{
-			/* several passes in one frame share the screen in the reference; composite their viewports */
-			size_t px = (size_t)w * h;
-			uint16_t *all = rc_malloc( px * 2 * rc.nviews );
-			RC_CHECK_DEV( rc_dev_render( rc.views, rc.nviews, w, h, 0, all, NULL ));
-			for( int i = 0; i < rc.nviews; i++ )
-			{
-				const int *vr = rc.views[i].vrect;
-				for( int y = vr[1]; y < vr[1] + vr[3] && y < h; y++ )
-					memcpy( rc.framebuf + (size_t)y * w + vr[0], all + px * i + (size_t)y * w + vr[0], (size_t)Q_min( vr[2], w - vr[0] ) * 2 );
-			}
-			rc_free( all );
-		}
+		/* the frames stay in HBM; the display conversion reads them there */
+		RC_CHECK_DEV( rc_dev_render( rc.views, rc.nviews, w, h, 0, NULL, NULL ));
 		rc_blit_screen();
 	}
 	rc.nviews = 0;
@@ -886,6 +899,13 @@ int RefCuda_BenchResident( int iters, int flags, float *ms_total, float *ms_stag
 int RefCuda_ReadSurfaceCache( int surf, int mip, unsigned short *out, int maxtexels, int *width, int *height, int *valid )
 {
 	return rc_dev_read_cache_block( surf, mip, out, maxtexels, width, height, valid );
+}
+
+int RefCuda_BlitViews( int first, int nviews, void *dst, unsigned int stride, unsigned int bpp, unsigned int rmask, unsigned int gmask, unsigned int bmask, float *ms_kernel )
+{
+	if( rc_set_display_format( bpp, rmask, gmask, bmask ))
+		return -1;
+	return rc_dev_blit( first, nviews, dst, stride, ms_kernel );
 }
 
 int RefCuda_GetCounters( unsigned long long *out, int n ) { return rc_dev_read_counters((uint64_t *)out, n ); }

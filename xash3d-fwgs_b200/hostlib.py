@@ -36,7 +36,7 @@ class Host:
     _copies = 0
     _loaded_refs: set = set()
 
-    def __init__(self, ref_path: str, width: int, height: int, cvars: dict | None = None):
+    def __init__(self, ref_path: str, width: int, height: int, cvars: dict | None = None, sw_format=None):
         if not os.path.exists(HOST_LIB_PATH):
             raise RuntimeError(f"{HOST_LIB_PATH} missing: run `python -c 'import __graft_entry__ as g; g.build()'`")
         if not os.path.exists(ref_path):
@@ -73,6 +73,13 @@ class Host:
         L.xh_add_brush_entity.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
         self.width, self.height = width, height
         self.ref_path = ref_path
+        # (bpp, rmask, gmask, bmask) of the software surface SW_CreateBuffer hands out; default RGB565
+        self.sw_format = tuple(sw_format) if sw_format else (2, 0xF800, 0x07E0, 0x001F)
+        L.xh_set_sw_format.argtypes = [C.c_uint] * 4
+        L.xh_set_sw_format(*self.sw_format)
+        L.xh_sw_buffer.restype = C.c_void_p
+        L.xh_sw_buffer.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.xh_soft_blit_views.argtypes = [C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
         for k, v in (cvars or {}).items():
             L.xh_cvar_set(k.encode(), str(v).encode())
         # renderers keep process-global state: a second instance of the same plugin in this process gets a
@@ -188,3 +195,23 @@ def pixels_to_rgb(buf: np.ndarray) -> np.ndarray:
     g = (((m >> 2) << 3) & 63) | (bit(j, 7) << 2) | (bit(j, 4) << 1) | bit(j, 1)
     b = ((m << 3) & 31) | (bit(j, 6) << 2) | (bit(j, 3) << 1) | bit(j, 0)
     return np.stack([r * 255 // 31, g * 255 // 63, b * 255 // 31], -1).astype(np.uint8)
+
+
+def screen_map(sw_format) -> np.ndarray:
+    """Numpy restatement of R_BuildScreenMap (ref/soft/r_glblit.c:347-407), test infrastructure: the 65536-entry table
+    pixel_t -> display pixel for sw_format = (bpp, rmask, gmask, bmask).  Entry (i << 8 | j) = major(i) | minor(j)."""
+    _, rmask, gmask, bmask = sw_format
+    shift = lambda m: (m & -m).bit_length() - 1 if m else 0
+    mult = lambda m: 1 << bin(m).count("1")
+    i = np.arange(256, dtype=np.uint64)
+    bit = lambda v, b: (v >> np.uint64(b)) & np.uint64(1)
+    scale = lambda c, m, d: ((c * np.uint64(mult(m))) // np.uint64(d)) << np.uint64(shift(m))
+    r = ((i >> np.uint64(5)) << np.uint64(2)) & np.uint64(31)
+    g = ((i >> np.uint64(2)) << np.uint64(3)) & np.uint64(63)
+    b = (i << np.uint64(3)) & np.uint64(31)
+    major = scale(r, rmask, 31) | scale(g, gmask, 63) | scale(b, bmask, 31)
+    r = (bit(i, 5) << np.uint64(1)) | bit(i, 2)
+    g = (bit(i, 7) << np.uint64(2)) | (bit(i, 4) << np.uint64(1)) | bit(i, 1)
+    b = (bit(i, 6) << np.uint64(2)) | (bit(i, 3) << np.uint64(1)) | bit(i, 0)
+    minor = scale(r, rmask, 31) | scale(g, gmask, 63) | scale(b, bmask, 31)
+    return (major[:, None] | minor[None, :]).reshape(65536).astype(np.uint32)

@@ -46,9 +46,9 @@ def make_map(which: str = "small", ncameras: int = 256, **kw):
 
 
 class Renderer:
-    def __init__(self, ref_path: str, width: int, height: int, gmap=None, cvars: dict | None = None):
+    def __init__(self, ref_path: str, width: int, height: int, gmap=None, cvars: dict | None = None, sw_format=None):
         self.is_cuda = ref_path == REF_CUDA_PATH or ref_path.endswith("libref_cuda.so") or ref_path.endswith("libref_cuda_emu.so")
-        self.host = Host(ref_path, width, height, cvars)
+        self.host = Host(ref_path, width, height, cvars, sw_format)
         self.width, self.height = width, height
         L = self.host.lib
         L.xh_soft_render_views.restype = C.c_double
@@ -61,6 +61,7 @@ class Renderer:
             self._counters = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int)(sym("RefCuda_GetCounters"))
             self._launches = C.CFUNCTYPE(C.c_ulonglong)(sym("RefCuda_LaunchCount"))
             self._devname = C.CFUNCTYPE(C.c_char_p)(sym("RefCuda_DeviceName"))
+            self._blit = C.CFUNCTYPE(C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.POINTER(C.c_float))(sym("RefCuda_BlitViews"))
         if gmap is not None:
             self.load_map(gmap)
 
@@ -119,6 +120,44 @@ class Renderer:
             if self.last_seconds < 0:
                 raise RuntimeError("not a ref_soft image")
         return color, z
+
+    def blit_views(self, cams, fov_x=90.0, sw_format=None, out=None):
+        """Display tail (R_BlitScreen): the views in the display format `sw_format` = (bpp, rmask, gmask, bmask)
+        (default: the format the host's software surface was created with) -> array[n,h,w] of uint16 / uint32.
+        CUDA: the batch is rendered, stays in HBM and is converted there (RefCuda_BlitViews).  Oracle: every view goes
+        through GL_RenderFrame + R_EndFrame and the software surface is copied out (its format is fixed at R_Init)."""
+        cams = np.asarray(cams, dtype=np.float32).reshape(-1, 6)
+        n = len(cams)
+        fmt = tuple(sw_format) if sw_format else self.host.sw_format
+        disp = out if out is not None else np.empty((n, self.height, self.width), np.uint16 if fmt[0] == 2 else np.uint32)
+        if self.is_cuda:
+            self.render_resident(cams, fov_x)
+            ms = C.c_float()
+            if self._blit(0, n, disp.ctypes.data, self.width, fmt[0], fmt[1], fmt[2], fmt[3], C.byref(ms)) != 0:
+                raise RuntimeError("RefCuda_BlitViews failed")
+            self.last_blit_ms = ms.value
+        else:
+            if fmt != self.host.sw_format:
+                raise ValueError("the oracle's display format is fixed when the renderer is created (sw_format=...)")
+            cc = np.ascontiguousarray(cams)
+            rc = self.host.lib.xh_soft_blit_views(cc.ctypes.data, n, fov_x, calc_fov_y(fov_x, self.width, self.height), 0, 0,
+                                                  self.width, self.height, RF_DRAW_WORLD, disp.ctypes.data)
+            if rc != 0:
+                raise RuntimeError(f"xh_soft_blit_views failed ({rc})")
+        return disp
+
+    def frame_views(self, cams, fov_x=90.0):
+        """The stock one-view-per-frame path the engine drives: R_BeginFrame, GL_RenderFrame, R_EndFrame per camera;
+        -> the software surface after each frame, array[n,h,w] in the host's display format."""
+        cams = np.ascontiguousarray(np.asarray(cams, dtype=np.float32).reshape(-1, 6))
+        n = len(cams)
+        disp = np.empty((n, self.height, self.width), np.uint16 if self.host.sw_format[0] == 2 else np.uint32)
+        L = self.host.lib
+        L.xh_frame_views.argtypes = [C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        if L.xh_frame_views(cams.ctypes.data, n, fov_x, calc_fov_y(fov_x, self.width, self.height), 0, 0, self.width, self.height,
+                            RF_DRAW_WORLD, disp.ctypes.data) != 0:
+            raise RuntimeError("xh_frame_views failed")
+        return disp
 
     def render_resident(self, cams, fov_x=90.0, clear=True):
         """Render with the results left in HBM (no device->host copy)."""
