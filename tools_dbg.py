@@ -13,3 +13,6 @@ print('events total', int(a[24]), 'max/line', int(a[25]))
 print(cu.counters())
 for i, name in enumerate(['stage', 'fatpvs', 'markleaves', 'P1', 'P2', 'P3', 'P4', 'P5']):
     print('vis', name, 'mean cycles/block', int(a[32 + 2 * i]) / 256, 'max', int(a[33 + 2 * i]))
+nb = 256 * 8
+for i, name in enumerate(['gather', 'keys', 'sort', 'localnum', 'count', 'fill']):
+    print('events', name, 'mean cycles/block', int(a[48 + i]) / nb, 'max', int(a[56 + i]))

@@ -489,7 +489,7 @@ int ensure_batch( int nviews, int width, int height )
 	WALLOC( ncands, int32_t, cap );
 	WALLOC( nedges, int32_t, cap );
 	w.nbands = ( height + SP_LINES - 1 ) / SP_LINES;
-	w.ev_ecap = width * height <= 640 * 480 ? 2048 : 4096;
+	w.ev_ecap = width * height <= 640 * 480 ? EV_ECAP_SMALL : EV_ECAP_BIG;
 	w.blk_events = SP_LINES * ( width / 2 > 512 ? width / 2 : 512 );
 	w.view_events = (size_t)w.nbands * w.blk_events;
 	w.scanbits = nullptr; w.scanbits_words = ( w.max_cands + 32 ) / 32;
@@ -561,7 +561,7 @@ int launch_slice( const rc_work_t &ws, cudaStream_t st, cudaEvent_t *evs, bool d
 	if( evs ) CK( cudaEventRecord( evs[3], st ));
 	const int nlines = ws.nviews * ws.height;
 	{
-		dim3 g( ws.nbands, ws.nviews );
+		dim3 g( ws.nviews, ws.nbands ); /* x = view: blocks are issued band by band, see k_events */
 		k_events<<<g, EV_THREADS, rc_events_smem( ws.ev_ecap, ws.scanbits_words ), st>>>( ws ); D.launches++;
 		const int lblocks = ( nlines + LN_WARPS - 1 ) / LN_WARPS;
 		k_lines<<<lblocks < LN_GRID ? lblocks : LN_GRID, LN_WARPS * 32, 0, st>>>( ws ); D.launches++;
@@ -646,7 +646,7 @@ int rc_dev_init( int device )
 	for( auto &ss : D.slice_stream ) CK( cudaStreamCreateWithFlags( &ss, cudaStreamNonBlocking ));
 	for( auto &e : D.ev ) CK( cudaEventCreate( &e ));
 	CK( cudaFuncSetAttribute( k_viswalk<VW_NTHREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 64 ));
-	CK( cudaFuncSetAttribute( k_events, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_events_smem( EV_ECAP_MAX, 65536 / 32 + 2 )));
+	CK( cudaFuncSetAttribute( k_events, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_events_smem( EV_ECAP_BIG, 65536 / 32 + 2 )));
 	CK( cudaFuncSetAttribute( k_draw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_draw_smem( 8192, 1 )));
 	for( int i = 0; i < 256; i++ ) D.h_styles[i] = 256;
 	if( upload( &D.d_styles, D.h_styles, 256 ) != 0 ) return -1;

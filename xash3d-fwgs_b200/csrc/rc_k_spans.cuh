@@ -34,9 +34,10 @@
 #error "k_events maps lanes to scanlines: SP_LINES must be 32"
 #endif
 
-/* band edges staged and pre-sorted in shared memory: w.ev_ecap of them (2048 for small frames, 4096 for big ones, where
- * a band of 32 lines is crossed by more edges); longer lists are read from the view's edge list in HBM, unsorted */
-#define EV_ECAP_MAX 8192 /* 13 bits of the presort key */
+/* band edges staged and pre-sorted in shared memory: w.ev_ecap of them (24 B each: the edge and its sort key); longer
+ * lists are read from the view's edge list in HBM, unsorted.  The presort key has 13 bits for the edge number. */
+#define EV_ECAP_SMALL 2048
+#define EV_ECAP_BIG   4096
 
 static inline size_t rc_events_smem( int32_t ecap, int32_t bitwords )
 {
@@ -54,7 +55,17 @@ __global__ void __launch_bounds__( EV_THREADS ) k_events( rc_work_t w )
 	uint32_t *s_bm = reinterpret_cast<uint32_t *>( ev_smem + ( sizeof( rc_edge_t ) + sizeof( unsigned long long )) * (size_t)w.ev_ecap );
 
 	const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-	const int band = blockIdx.x, view = blockIdx.y, nbands = gridDim.x;
+	/* bands are issued from the middle of the frame outwards: the horizon of an indoor view is where the edges are
+	 * (bands with 600 edges next to bands with 30), and the longest blocks should start first */
+	const int view = blockIdx.x, nbands = gridDim.y;
+	const int band = ( nbands >> 1 ) + (( blockIdx.y & 1 ) ? -(int)(( blockIdx.y + 1 ) >> 1 ) : (int)( blockIdx.y >> 1 ));
+#ifdef RC_SPANS_DEBUG
+	long long ev_t[10]; int ev_n = 0;
+#define EV_MARK() do { __syncthreads(); ev_t[ev_n++] = clock64(); } while( 0 )
+#else
+#define EV_MARK() do { } while( 0 )
+#endif
+	EV_MARK();
 	const rc_view_t *vw = &w.views[view];
 	const int32_t y0 = vw->vrect[1], vw_h = vw->vrect[3];
 	const int32_t y = band * SP_LINES + lane;
@@ -97,11 +108,11 @@ __global__ void __launch_bounds__( EV_THREADS ) k_events( rc_work_t w )
 		}
 	}
 	__syncthreads();
+	EV_MARK(); /* 1: gathered */
 	/* more edges than the staging area holds: the lines read the view's edge list from HBM, unsorted */
 	const bool staged = s_ne <= w.ev_ecap;
 	if( t == 0 && !staged ) atomicAdd( &w.counters[RC_CTR_UNSTAGED_BANDS], 1ull );
 	const int32_t ne = staged ? s_ne : nview;
-	const rc_edge_t *E = staged ? s_edge : vedges;
 	int32_t npow = 32;
 	while( npow < ne ) npow <<= 1;
 	const int32_t ymid = band * SP_LINES + SP_LINES / 2;
@@ -119,8 +130,21 @@ __global__ void __launch_bounds__( EV_THREADS ) k_events( rc_work_t w )
 		}
 	__syncthreads();
 
+	EV_MARK(); /* 2: keys */
 	/* B. block bitonic sort of the keys: the order the lines will (nearly) need */
-	if( staged && ne > 1 )
+	if( staged && ne > 1 && ne <= EV_THREADS )
+	{
+		/* short lists (the usual case): rank sort - every thread counts the keys below its own (broadcast reads,
+		 * no barriers inside), keys are unique (the edge number is part of them) */
+		const unsigned long long mine = t < ne ? s_key[t] : 0ull;
+		int32_t rank = 0;
+		if( t < ne )
+			for( int32_t i = 0; i < ne; i++ ) rank += s_key[i] < mine ? 1 : 0;
+		__syncthreads();
+		if( t < ne ) s_key[rank] = mine;
+		__syncthreads();
+	}
+	else if( staged && ne > 1 )
 		for( int32_t k = 2; k <= npow; k <<= 1 )
 			for( int32_t j = k >> 1; j > 0; j >>= 1 )
 			{
@@ -133,6 +157,7 @@ __global__ void __launch_bounds__( EV_THREADS ) k_events( rc_work_t w )
 				__syncthreads();
 			}
 
+	EV_MARK(); /* 3: sorted */
 	/* C. band-local surface numbers: rank of the surface among those present in the band, + 1 (order preserving, so
 	 * "lowest set bit = smallest key" still holds in k_lines, with far fewer bit-set words) */
 	int32_t carry = 0;
@@ -170,14 +195,44 @@ __global__ void __launch_bounds__( EV_THREADS ) k_events( rc_work_t w )
 		bsurf[0] = 0;
 		w.bandnloc[view * nbands + band] = nlocal;
 	}
+	/* the staged edges are permuted into sorted order (through registers: all reads, barrier, all writes) with the
+	 * band-local surface number in the lead / trail half of surfs: the per-line loops below then read one 16-byte
+	 * record per edge and nothing else */
+	if( staged )
+	{
+		rc_edge_t mine[EV_ECAP_BIG / EV_THREADS];
+#pragma unroll
+		for( int q = 0; q < EV_ECAP_BIG / EV_THREADS; q++ )
+		{
+			const int32_t k = q * EV_THREADS + t;
+			if( k < ne )
+			{
+				rc_edge_t e = s_edge[(int32_t)( (uint32_t)s_key[k] & 8191u )];
+				const uint32_t tr = e.surfs & 0xFFFF, s = tr ? tr : ( e.surfs >> 16 );
+				const uint32_t loc = s_pre[s >> 5] + (uint32_t)__popc( s_bm[s >> 5] & (( 1u << ( s & 31 )) - 1u )) + 1u;
+				e.surfs = tr ? loc : ( loc << 16 );
+				mine[q] = e;
+			}
+		}
+		__syncthreads();
+#pragma unroll
+		for( int q = 0; q < EV_ECAP_BIG / EV_THREADS; q++ )
+		{
+			const int32_t k = q * EV_THREADS + t;
+			if( k < ne ) s_edge[k] = mine[q];
+		}
+		__syncthreads();
+	}
+	const rc_edge_t *L = staged ? s_edge : vedges;
 
+	EV_MARK(); /* 4: local numbers */
 	/* 1. events per line: every warp takes a contiguous run of the sorted edge list */
 	const int32_t per = ( ne + EV_WARPS - 1 ) / EV_WARPS;
 	const int32_t k0 = warp * per, k1 = min( ne, k0 + per );
 	int32_t cnt = 0;
 	for( int32_t k = k0; k < k1; k++ )
 	{
-		const uint32_t vv = E[staged ? (int32_t)( (uint32_t)s_key[k] & 8191u ) : k].vv;
+		const uint32_t vv = L[k].vv;
 		cnt += ( valid && y >= (int32_t)( vv & 0xFFFF ) && y <= (int32_t)( vv >> 16 )) ? 1 : 0;
 	}
 	s_wcnt[warp][lane] = cnt;
@@ -207,22 +262,42 @@ __global__ void __launch_bounds__( EV_THREADS ) k_events( rc_work_t w )
 		if( y < w.height )
 			w.lineinfo[(size_t)view * w.height + y] = li;
 	}
+	EV_MARK(); /* 5: counted */
+#ifndef RC_SPANS_DEBUG
 	if( !valid || !fits )
 		return;
+#endif
 
 	/* 2. the events, surfaces renumbered band-locally */
 	int32_t pos = off + mybase;
+#ifdef RC_SPANS_DEBUG
+	if( valid && fits )
+#endif
 	for( int32_t k = k0; k < k1; k++ )
 	{
-		const rc_edge_t e = E[staged ? (int32_t)( (uint32_t)s_key[k] & 8191u ) : k];
+		const rc_edge_t e = L[k];
 		const int32_t v = (int32_t)( e.vv & 0xFFFF );
 		if( y >= v && y <= (int32_t)( e.vv >> 16 ))
 		{
-			const uint32_t tr = e.surfs & 0xFFFF, s = tr ? tr : ( e.surfs >> 16 );
-			const uint32_t loc = s_pre[s >> 5] + (uint32_t)__popc( s_bm[s >> 5] & (( 1u << ( s & 31 )) - 1u )) + 1u;
-			arena[pos++] = rc_event_key( (int32_t)((uint32_t)e.u + (uint32_t)( y - v ) * (uint32_t)e.u_step ), tr ? loc : ( loc << 16 ));
+			uint32_t both = e.surfs;
+			if( !staged )
+			{
+				const uint32_t tr = e.surfs & 0xFFFF, s = tr ? tr : ( e.surfs >> 16 );
+				const uint32_t loc = s_pre[s >> 5] + (uint32_t)__popc( s_bm[s >> 5] & (( 1u << ( s & 31 )) - 1u )) + 1u;
+				both = tr ? loc : ( loc << 16 );
+			}
+			arena[pos++] = rc_event_key( (int32_t)((uint32_t)e.u + (uint32_t)( y - v ) * (uint32_t)e.u_step ), both );
 		}
 	}
+	EV_MARK(); /* 6: filled */
+#ifdef RC_SPANS_DEBUG
+	if( t == 0 )
+		for( int k = 0; k < 6; k++ )
+		{
+			atomicAdd( &w.counters[48 + k], (unsigned long long)( ev_t[k + 1] - ev_t[k] ));
+			atomicMax( &w.counters[56 + k], (unsigned long long)( ev_t[k + 1] - ev_t[k] ));
+		}
+#endif
 }
 
 /* bitonic sort of n <= SP_SORTCAP keys in shared memory by one warp; buf holds the keys padded to a power of two */
