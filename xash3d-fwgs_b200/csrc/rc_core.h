@@ -500,6 +500,26 @@ RC_HD void rc_render_face( const rc_scene_t *sc, const rc_view_t *vw, const rc_c
 	fs->u1 = fs->v1 = fs->lzi1 = 0; fs->ceilv1 = 0;
 	int makeleftedge = 0, makerightedge = 0;
 
+	if( sc->sedgeverts )
+	{
+		/* both vertices of every surfedge were laid out per surfedge at upload: one load per edge, the next edge's
+		 * issued before this one is clipped */
+		const float *sv = sc->sedgeverts + (size_t)sf->firstedge * 6;
+		float cur[6], nxt[6];
+		for( int k = 0; k < 6; k++ ) cur[k] = sf->numedges > 0 ? sv[k] : 0.0f;
+		for( int32_t i = 0; i < sf->numedges; i++ )
+		{
+			if( i + 1 < sf->numedges )
+				for( int k = 0; k < 6; k++ ) nxt[k] = sv[( i + 1 ) * 6 + k];
+			fs->leftclipped = fs->rightclipped = 0;
+			rc_clip_edge( vw, fs, cur, cur + 3, planes, nplanes, 0 );
+			if( fs->leftclipped ) makeleftedge = 1;
+			if( fs->rightclipped ) makerightedge = 1;
+			fs->lastvertvalid = 1;
+			for( int k = 0; k < 6; k++ ) cur[k] = nxt[k];
+		}
+	}
+	else
 	for( int32_t i = 0; i < sf->numedges; i++ )
 	{
 		int32_t lindex = sc->surfedges[sf->firstedge + i];

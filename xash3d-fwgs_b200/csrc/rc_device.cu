@@ -94,10 +94,12 @@ __device__ __forceinline__ int32_t rc_warp_incl_scan( int32_t x, int lane )
 /* ---------------------------------------------------------------------------------------------- */
 /* S1: faces -> surf_t records + edges                                                               */
 
-__global__ void __launch_bounds__( 128 ) k_faces( rc_scene_t sc, rc_work_t w )
+#define FC_THREADS 64
+
+__global__ void __launch_bounds__( FC_THREADS ) k_faces( rc_scene_t sc, rc_work_t w )
 {
-	const int view = blockIdx.y;
-	const int ci = blockIdx.x * blockDim.x + threadIdx.x;
+	const int view = blockIdx.x;
+	const int ci = blockIdx.y * blockDim.x + threadIdx.x;
 	if( ci >= w.ncands[view] )
 		return;
 	const rc_view_t *vw = &w.views[view];
@@ -139,16 +141,21 @@ __global__ void __launch_bounds__( 128 ) k_faces( rc_scene_t sc, rc_work_t w )
 		fs.out[k].u = 0; fs.out[k].u_step = 0; fs.out[k].vv = 1u; fs.out[k].surfs = 0;
 	}
 
-	if( o.emitted )
+	if( o.emitted && !( o.flags & ( RC_SURF_DRAWSKY | RC_SURF_DRAWTURB )) && o.cache_ofs >= 0 )
 	{
-		atomicAdd( &w.counters[RC_CTR_SURFS], 1ull );
-		if( !( o.flags & ( RC_SURF_DRAWSKY | RC_SURF_DRAWTURB )) && o.cache_ofs >= 0 )
+		int32_t slot = cand.surf * 4 + o.miplevel;
+		atomicOr( &w.cache_need[slot >> 5], 1u << ( slot & 31 ));
+	}
+	/* batch counters: one atomic per warp (tens of thousands of threads adding to one address serialise in L2) */
+	{
+		const unsigned m = __activemask();
+		const unsigned ns = __reduce_add_sync( m, o.emitted ? 1u : 0u ), ne = __reduce_add_sync( m, (unsigned)nout );
+		if(( threadIdx.x & 31 ) == __ffs( (int)m ) - 1 )
 		{
-			int32_t slot = cand.surf * 4 + o.miplevel;
-			atomicOr( &w.cache_need[slot >> 5], 1u << ( slot & 31 ));
+			if( ns ) atomicAdd( &w.counters[RC_CTR_SURFS], (unsigned long long)ns );
+			if( ne ) atomicAdd( &w.counters[RC_CTR_EDGES], (unsigned long long)ne );
 		}
 	}
-	atomicAdd( &w.counters[RC_CTR_EDGES], (unsigned long long)nout );
 }
 
 /* ---------------------------------------------------------------------------------------------- */
@@ -549,8 +556,10 @@ int launch_slice( const rc_work_t &ws, cudaStream_t st, cudaEvent_t *evs, bool d
 	D.launches++;
 	if( evs ) CK( cudaEventRecord( evs[1], st ));
 	{
-		dim3 g(( ws.max_cands + 127 ) / 128, ws.nviews );
-		k_faces<<<g, 128, 0, st>>>( sc, ws ); D.launches++;
+		/* x = view: the blocks that have candidates (the first chunks of every view) are issued first, ahead of the
+		 * thousands of empty ones (max_cands is the face count of the map) */
+		dim3 g( ws.nviews, ( ws.max_cands + FC_THREADS - 1 ) / FC_THREADS );
+		k_faces<<<g, FC_THREADS, 0, st>>>( sc, ws ); D.launches++;
 	}
 	if( evs ) CK( cudaEventRecord( evs[2], st ));
 	{
@@ -749,8 +758,27 @@ int rc_dev_upload_scene( const rc_scene_t *sc, size_t cache_texels )
 			if( sc->surfaces[i].flags & RC_SURF_PLANEBACK ) sb[i >> 5] |= 1u << ( i & 31 );
 		if( upload( &surfback, sb.data(), sb.size()) != 0 ) return -1;
 	}
-	D.d_scene[11] = pvsdense; D.d_scene[12] = surfnode; D.d_scene[13] = surfback;
-	d.pvsdense = pvsdense; d.surfnode = surfnode; d.surfback = surfback;
+	float *sedgeverts = (float *)D.d_scene[14];
+	{
+		std::vector<float> sv((size_t)( sc->numsurfedges > 0 ? sc->numsurfedges : 1 ) * 6, 0.0f );
+		for( int32_t i = 0; i < sc->numsurfedges; i++ )
+		{
+			int32_t l = sc->surfedges[i];
+			const int a = l > 0 ? 0 : 1;
+			if( l < 0 ) l = -l;
+			if( l >= sc->numedges ) continue;
+			const int32_t i0 = sc->edges[2 * l + a], i1 = sc->edges[2 * l + ( a ^ 1 )];
+			if( i0 >= sc->numverts || i1 >= sc->numverts ) continue;
+			for( int k = 0; k < 3; k++ )
+			{
+				sv[(size_t)i * 6 + k] = sc->verts[3 * i0 + k];
+				sv[(size_t)i * 6 + 3 + k] = sc->verts[3 * i1 + k];
+			}
+		}
+		if( upload( &sedgeverts, sv.data(), sv.size()) != 0 ) return -1;
+	}
+	D.d_scene[11] = pvsdense; D.d_scene[12] = surfnode; D.d_scene[13] = surfback; D.d_scene[14] = sedgeverts;
+	d.pvsdense = pvsdense; d.surfnode = surfnode; d.surfback = surfback; d.sedgeverts = sedgeverts;
 	D.d_scene[0] = planes; D.d_scene[1] = nodes; D.d_scene[2] = leafs; D.d_scene[3] = surfaces; D.d_scene[4] = marks;
 	D.d_scene[5] = surfedges; D.d_scene[6] = edges; D.d_scene[7] = verts; D.d_scene[8] = visdata; D.d_scene[9] = lightdata;
 	D.d_scene[10] = cache;

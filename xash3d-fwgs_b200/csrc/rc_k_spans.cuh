@@ -24,7 +24,7 @@
 #define EV_WARPS    ( EV_THREADS / 32 )
 #define LN_WARPS    4
 #define LN_HEAVY    64   /* events: lines above go first */
-#define LN_CHUNK    4    /* scanlines a warp takes from the shared cursor at a time */
+#define LN_CHUNK    1    /* scanlines a warp takes from the shared cursor at a time (measured on the C2 batch: 1: 170 us, 2: 172, 4: 183, 8: 184) */
 #define SP_SORTCAP  512  /* events per line the shared-memory sorter takes; longer lines fall back to a serial sort */
 #define SP_BITWORDS 64   /* shared-memory bit-set words per line (views listing <= 2015 faces), else global scratch */
 #define SP_EXCCAP   8
@@ -443,8 +443,7 @@ __global__ void __launch_bounds__( LN_WARPS * 32, 8 ) k_lines( rc_work_t w )
 	/* scanlines differ a lot in cost (2 .. 500 events) and the heavy ones cluster (the horizon of corridor views):
 	 * warps draw them from a shared cursor, view-interleaved */
 	/* two sweeps over the lines: the heavy ones first (longest processing time first keeps the tail short) */
-	/* lines per cursor grab: LN_CHUNK when every warp gets many lines, one when lines are few and long (big frames) */
-	const int32_t chunk = nlines >= (int32_t)gridDim.x * LN_WARPS * 8 ? LN_CHUNK : 1;
+	const int32_t chunk = LN_CHUNK;
 	for( int32_t q = 0, heavy = 1; ; q++ )
 	{
 		int32_t item = 0;

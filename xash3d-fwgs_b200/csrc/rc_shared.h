@@ -109,6 +109,8 @@ typedef struct
 	const uint32_t     *pvsdense;  /* [numleafs][visbytes_padded / 4] Mod_DecompressPVS of every leaf's row */
 	const int32_t      *surfnode;  /* [numsurfaces] the node a surface hangs off */
 	const uint32_t     *surfback;  /* [numsurfaces bits] SURF_PLANEBACK */
+	const float        *sedgeverts;/* [numsurfedges][6] both vertices of every surfedge in its winding direction: one load
+	                                * instead of the surfedges -> edges -> verts chain of three dependent ones */
 } rc_scene_t;
 
 /* per-view constants: everything R_SetupFrustum/R_SetupFrameQ/R_ViewChanged/R_TransformFrustum derive
