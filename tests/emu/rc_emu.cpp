@@ -53,7 +53,7 @@ void build_block( int s, int mip )
 	int smax = sf->lightextents[0] / sf->sample_size + 1, tmax = sf->lightextents[1] / sf->sample_size + 1;
 	std::vector<uint32_t> bl( smax * tmax );
 	for( int i = 0; i < smax * tmax; i++ )
-		bl[i] = rc_blocklight( &E.sc, sf, E.styles, smax * tmax, i );
+		bl[i] = rc_blocklight( &E.sc, sf, E.styles, smax * tmax, i, 0u );
 	int w = sf->lightextents[0] >> mip, h = sf->lightextents[1] >> mip;
 	uint16_t *dst = E.cache.data() + sf->cache_ofs[mip];
 	for( int y = 0; y < h; y++ )
@@ -262,6 +262,9 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 	}
 	return 0;
 }
+
+/* dynamic lights are not part of the debug harness */
+int rc_dev_set_dlights( const rc_dlight_t *, int n ) { return n ? -1 : 0; }
 
 /* the display tail is not part of the debug harness (it keeps no frames) */
 int rc_dev_set_screenmap( const uint32_t *, int ) { return 0; }

@@ -296,3 +296,39 @@ def test_display_tail_ragged_frame_size(pkg, scene):
     so = scene.Renderer(pkg.REF_SOFT_PATH, 322, 241, m)
     cu = scene.Renderer(pkg.REF_CUDA_PATH, 322, 241, m)
     assert np.array_equal(cu.blit_views(m.cameras[:5]), so.blit_views(m.cameras[:5]))
+
+
+@pytest.mark.gpu
+def test_dynamic_lights_match_reference(pkg, scene):
+    """R_PushDlights / R_MarkLights / R_AddDynamicLights (ref/common/ref_light.c:93-185, ref/soft/r_surf.c:72-165):
+    lit frames and the lit surface-cache blocks are bit-identical, and the frames return to the unlit ones when the
+    lights are switched off (a block built with a dynamic light is never reused)."""
+    m = scene.make_map("small", ncameras=32)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    cu = scene.Renderer(pkg.REF_CUDA_PATH, 320, 240, m)
+    cams = np.asarray(m.cameras[:12], dtype=np.float32)
+    base_c, base_z = so.render_views(cams)
+    got_c, got_z = cu.render_views(cams)
+    assert np.array_equal(got_c, base_c) and np.array_equal(got_z, base_z)
+    for r in (so, cu):
+        r.set_dlight(0, cams[0][:3], 300.0, (255, 200, 150))
+        r.set_dlight(3, cams[5][:3] + np.array([0, 0, 20], np.float32), 200.0, (80, 120, 255), minlight=16.0)
+        r.set_dlight(7, cams[9][:3] + np.array([30, -10, 0], np.float32), 120.0, (255, 255, 255), die=-1.0)  # dead
+    lit_c, lit_z = so.render_views(cams)
+    got_c, got_z = cu.render_views(cams)
+    assert (lit_c != base_c).mean() > 0.01, "the oracle did not respond to the lights"
+    assert np.array_equal(got_c, lit_c) and np.array_equal(got_z, lit_z)
+    checked = 0
+    for s in range(so.host.world_info()["numsurfaces"]):
+        for mip in range(4):
+            a, b = so.cache_block(s, mip), cu.cache_block(s, mip)
+            if a is not None and b is not None:
+                assert np.array_equal(a, b), (s, mip)
+                checked += 1
+    assert checked > 0
+    for r in (so, cu):
+        r.set_dlight(0, cams[0][:3], 0.0)
+        r.set_dlight(3, cams[5][:3], 0.0)
+    off_c, _ = so.render_views(cams)
+    got_c, _ = cu.render_views(cams)
+    assert np.array_equal(off_c, base_c) and np.array_equal(got_c, base_c)

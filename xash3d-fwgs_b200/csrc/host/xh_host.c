@@ -553,6 +553,20 @@ int xh_frame_views( const float *cams, int n, float fov_x, float fov_y, int x, i
 	return 0;
 }
 
+/* an entry of the engine's dynamic light table (CL_AllocDlight, engine/client/cl_efx.c); radius 0 switches it off */
+int xh_set_dlight( int i, const float *origin, float radius, int r, int g, int b, float die, float minlight )
+{
+	if( i < 0 || i >= MAX_DLIGHTS )
+		return -1;
+	dlight_t *l = &xh.dlights[i];
+	memset( l, 0, sizeof( *l ));
+	for( int k = 0; k < 3; k++ ) l->origin[k] = origin[k];
+	l->radius = radius; l->die = die; l->minlight = minlight;
+	l->color.r = (uint8_t)r; l->color.g = (uint8_t)g; l->color.b = (uint8_t)b;
+	l->key = i + 1;
+	return 0;
+}
+
 void xh_clear_scene( void ) { xh.ref.R_ClearScene(); }
 
 int xh_add_brush_entity( int modelindex, const float *origin, const float *angles, int rendermode, int renderamt )

@@ -73,6 +73,8 @@ XH_EXPORT double xh_soft_render_views( const float *cams, int n, float fov_x, fl
  * surface itself (what R_EndFrame wrote) */
 XH_EXPORT void xh_set_sw_format( unsigned bpp, unsigned rmask, unsigned gmask, unsigned bmask );
 XH_EXPORT const void *xh_sw_buffer( int *w, int *h, int *bpp );
+/* entry i of the engine's dynamic light table (PARM_GET_DLIGHTS_PTR); radius 0 = off; alive while die >= time */
+XH_EXPORT int xh_set_dlight( int i, const float *origin, float radius, int r, int g, int b, float die, float minlight );
 /* the engine's frame loop, one view per frame (R_BeginFrame, GL_RenderFrame, R_EndFrame), any renderer plugin */
 XH_EXPORT int xh_frame_views( const float *cams, int n, float fov_x, float fov_y, int x, int y, int w, int h, int flags, void *display_out );
 /* oracle-only: the views one by one through GL_RenderFrame + R_EndFrame (R_BlitScreen); surface copied out per view */

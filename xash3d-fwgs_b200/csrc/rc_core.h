@@ -988,8 +988,57 @@ RC_HD int16_t rc_pixel_z( const rc_chunk_t *c, int32_t i )
 /* ------------------------------------------------------------------------------------------ */
 /* A7/A8: light map blend and surface cache block (ref/soft/r_surf.c:174-229,291-757)            */
 
-/* R_BuildLightMap for luxel i of a face: sum of (r+g+b) * style value, gamma, quantise to bits 8..12 */
-RC_HD uint32_t rc_blocklight( const rc_scene_t *sc, const rc_surface_t *sf, const int32_t *stylevalue, int32_t size, int32_t i )
+/*
+ * R_AddDynamicLights (ref/soft/r_surf.c:72-165) for luxel (s, t) of a world face: what the lights whose bit is set
+ * in `bits` add to blocklights[s + t * smax].  World faces only (tr.modelviewIdentity), sample_frac 1 (no
+ * TEX_WORLD_LUXELS).  The per-light constants are recomputed per luxel; float expressions in the reference's order.
+ */
+RC_HD uint32_t rc_dlight_luxel( const rc_scene_t *sc, const rc_surface_t *sf, const rc_dlight_t *lights, int32_t nlights, uint32_t bits, int32_t s, int32_t t )
+{
+	const rc_plane_t *pl = &sc->planes[sf->plane];
+	const float sample_size = (float)sf->sample_size;
+	uint32_t add = 0;
+	for( int32_t k = 0; k < nlights; k++ )
+	{
+		const rc_dlight_t *dl = &lights[k];
+		if( !( bits & ( 1u << dl->bit )))
+			continue;
+		float rad = dl->radius;
+		const float dist = rc_planediff( dl->origin, pl );
+		rad -= dist < 0 ? -dist : dist;
+		float minlight = dl->minlight;
+		if( rad < minlight )
+			continue;
+		minlight = rad - minlight;
+		float impact[3];
+		if( pl->type < 3 )
+		{
+			impact[0] = dl->origin[0]; impact[1] = dl->origin[1]; impact[2] = dl->origin[2];
+			impact[pl->type] -= dist;
+		}
+		else
+		{
+			const float nd = -dist;
+			impact[0] = dl->origin[0] + nd * pl->normal[0];
+			impact[1] = dl->origin[1] + nd * pl->normal[1];
+			impact[2] = dl->origin[2] + nd * pl->normal[2];
+		}
+		const float sl = rc_dot3( impact, sf->lmvecs[0] ) + sf->lmvecs[0][3] - (float)sf->lightmapmins[0];
+		const float tl = rc_dot3( impact, sf->lmvecs[1] ) + sf->lmvecs[1][3] - (float)sf->lightmapmins[1];
+		int32_t td = rc_f2i(( tl - sample_size * (float)t ) * 1.0f );
+		if( td < 0 ) td = -td;
+		int32_t sd = rc_f2i(( sl - sample_size * (float)s ) * 1.0f );
+		if( sd < 0 ) sd = -sd;
+		const float d = sd > td ? (float)( sd + ( td >> 1 )) : (float)( td + ( sd >> 1 ));
+		if( d < minlight )
+			add += (uint32_t)(( rc_f2i(( rad - d ) * 256.0f ) * dl->monolight ) / 256 );
+	}
+	return add;
+}
+
+/* R_BuildLightMap for luxel i of a face: sum of (r+g+b) * style value, dynamic lights (`extra`, rc_dlight_luxel),
+ * gamma, quantise to bits 8..12 */
+RC_HD uint32_t rc_blocklight( const rc_scene_t *sc, const rc_surface_t *sf, const int32_t *stylevalue, int32_t size, int32_t i, uint32_t extra )
 {
 	uint32_t bl = 0;
 	if( sf->lightofs >= 0 )
@@ -1003,6 +1052,7 @@ RC_HD uint32_t rc_blocklight( const rc_scene_t *sc, const rc_surface_t *sf, cons
 			bl += ((uint32_t)lm[0] + lm[1] + lm[2] ) * scale;
 		}
 	}
+	bl += extra;
 	int32_t t;
 	if( bl < 65280 )
 	{

@@ -29,6 +29,9 @@ int rc_dev_upload_scene( const rc_scene_t *sc, size_t cache_texels );
 int rc_dev_update_surface_texnums( const int32_t *texnum, int n );
 /* g_lightstylevalue[256] for the next batch (ref/common/ref_light.c:30-87) */
 int rc_dev_set_lightstyles( const int32_t *values );
+/* the active dynamic lights of the next batches (R_PushDlights, ref/common/ref_light.c:170: die >= time, radius != 0);
+ * marks the world faces each one reaches (R_MarkLights) on the device.  n = 0: none */
+int rc_dev_set_dlights( const rc_dlight_t *lights, int n );
 /* drop every cached block (D_FlushCaches, ref/soft/r_surf.c:810) */
 int rc_dev_flush_cache( void );
 

@@ -32,7 +32,8 @@ struct rc_cachekey_t
 	int32_t texnum;
 	int32_t light[RC_MAXLIGHTMAPS];
 	int32_t valid;
-	int32_t pad[2];
+	int32_t dlight; /* surfcache_t.dlight: built with dynamic lights, never reused (r_surf.c:1099,1149) */
+	int32_t pad;
 }; /* 32 B: what D_CacheSurface compares (r_surf.c:1090-1120): texture, light style values */
 
 struct rc_lineinfo_t { int32_t ofs, nsp; }; /* span slice of a scanline: first slot inside the view's arena, count */
@@ -56,6 +57,9 @@ struct rc_work_t
 	int32_t   *cache_nlist, *cache_cursor;
 	int32_t   *line_cursor; /* k_lines work cursor */
 	const int32_t *styles;/* [256] g_lightstylevalue */
+	const rc_dlight_t *dlights; /* active dynamic lights of the batch */
+	const uint32_t *dlightbits; /* [numsurfaces] msurface_t.dlightbits (k_dlight_mark) */
+	int32_t ndlights;
 	uint32_t  *scanbits;  /* surface bit sets of k_spans when a view lists > 2015 faces, else NULL */
 	int32_t    scanbits_words, nbands;
 	uint16_t  *bandsurf;  /* [nviews][nbands][max_cands + 2] band-local surface number -> candidate index + 1 */
@@ -181,7 +185,8 @@ __global__ void __launch_bounds__( 256 ) k_cache_list( rc_scene_t sc, rc_work_t 
 	const rc_surface_t *sf = &sc.surfaces[slot >> 2];
 	if( sf->cache_ofs[slot & 3] < 0 )
 		return;
-	if( rc_key_stale( &w.cache_keys[slot], sf, w.styles ))
+	/* a face lit by a dynamic light is rebuilt every frame, and so is a block that was built with one */
+	if( rc_key_stale( &w.cache_keys[slot], sf, w.styles ) || w.cache_keys[slot].dlight || ( w.ndlights && w.dlightbits[slot >> 2] ))
 		w.cache_list[atomicAdd( w.cache_nlist, 1 )] = slot;
 }
 
@@ -262,8 +267,17 @@ __global__ void __launch_bounds__( CACHE_THREADS ) k_cache_build( rc_scene_t sc,
 			if( tid == 0 ) atomicAdd( &w.counters[RC_CTR_OVERFLOW_CANDS], 1ull );
 			continue;
 		}
+		const uint32_t dbits = w.ndlights ? w.dlightbits[slot >> 2] : 0u;
 		for( int32_t i = tid; i < size; i += CACHE_THREADS )
-			s_bl[i] = rc_blocklight( &sc, sf, w.styles, size, i );
+		{
+			uint32_t extra = 0;
+			if( dbits )
+			{
+				const int32_t lt = i / smax;
+				extra = rc_dlight_luxel( &sc, sf, w.dlights, w.ndlights, dbits, i - lt * smax, lt );
+			}
+			s_bl[i] = rc_blocklight( &sc, sf, w.styles, size, i, extra );
+		}
 
 		const int32_t bw = sf->lightextents[0] >> mip, bh = sf->lightextents[1] >> mip;
 		const int32_t k = 4 - mip, bs = 16 >> mip;
@@ -319,6 +333,7 @@ __global__ void __launch_bounds__( CACHE_THREADS ) k_cache_build( rc_scene_t sc,
 			for( int j = 0; j < RC_MAXLIGHTMAPS; j++ )
 				kk->light[j] = sf->styles[j] != 255 ? w.styles[sf->styles[j]] : 0;
 			kk->valid = 1;
+			kk->dlight = dbits ? 1 : 0;
 			atomicAdd( &w.counters[RC_CTR_CACHE_BLOCKS], 1ull );
 			atomicAdd( &w.counters[RC_CTR_CACHE_TEXELS], (unsigned long long)bw * bh );
 		}
@@ -332,6 +347,70 @@ __global__ void __launch_bounds__( CACHE_THREADS ) k_cache_build( rc_scene_t sc,
 /* host side of the C layer                                                                          */
 
 namespace {
+
+/* ---------------------------------------------------------------------------------------------- */
+/* R_PushDlights / R_MarkLights (ref/common/ref_light.c:93-185) for the world: thread per surface.  The recursion
+ * reaches the node a surface hangs off iff at every ancestor the light's distance to the split plane does not send
+ * it down the other side only; at the node itself the reference's plane-distance and clamped-impact tests apply.    */
+
+__global__ void __launch_bounds__( 128 ) k_dlight_mark( rc_scene_t sc, const rc_dlight_t *lights, int32_t nlights, uint32_t *bits )
+{
+	const int s = blockIdx.x * blockDim.x + threadIdx.x;
+	if( s >= sc.numsurfaces )
+		return;
+	const rc_surface_t *sf = &sc.surfaces[s];
+	const int32_t n0 = sc.surfnode[s];
+	uint32_t out = 0;
+	/* a surface no node lists is never marked (surfnode defaults to 0 for those: check the range) */
+	const bool listed = s >= sc.nodes[n0].firstsurface && s < sc.nodes[n0].firstsurface + sc.nodes[n0].numsurfaces;
+	for( int32_t k = 0; k < nlights && listed; k++ )
+	{
+		const rc_dlight_t *dl = &lights[k];
+		const float vr = dl->virtual_radius, maxdist = dl->radius * dl->radius;
+		const float dist = rc_planediff( dl->origin, &sc.planes[sc.nodes[n0].plane] );
+		if( dist > vr || dist < -vr )
+			continue; /* the walk passes this node without looking at its surfaces */
+		const float dist_sq = dist * dist;
+		if( !( dist_sq < maxdist ))
+			continue;
+		bool reach = true;
+		for( int32_t c = n0, a = sc.nodes[n0].parent; a >= 0 && reach; c = a, a = sc.nodes[a].parent )
+		{
+			const float d = rc_planediff( dl->origin, &sc.planes[sc.nodes[a].plane] );
+			if( d > vr ) reach = sc.nodes[a].child[0] == c;
+			else if( d < -vr ) reach = sc.nodes[a].child[1] == c;
+		}
+		if( !reach )
+			continue;
+		const rc_plane_t *pl = &sc.planes[sf->plane];
+		float impact[3];
+		if( pl->type < 3 )
+		{
+			impact[0] = dl->origin[0]; impact[1] = dl->origin[1]; impact[2] = dl->origin[2];
+			impact[pl->type] -= dist;
+		}
+		else
+		{
+			const float nd = -dist;
+			impact[0] = dl->origin[0] + nd * pl->normal[0];
+			impact[1] = dl->origin[1] + nd * pl->normal[1];
+			impact[2] = dl->origin[2] + nd * pl->normal[2];
+		}
+		/* clamp the centre of the light to the face and check the brightness there */
+		float l = rc_dot3( impact, sf->lmvecs[0] ) + sf->lmvecs[0][3] - (float)sf->lightmapmins[0];
+		float sx = l + 0.5f;
+		sx = sx >= 0 ? ( sx < (float)sf->lightextents[0] ? sx : (float)sf->lightextents[0] ) : 0;
+		sx = l - sx;
+		l = rc_dot3( impact, sf->lmvecs[1] ) + sf->lmvecs[1][3] - (float)sf->lightmapmins[1];
+		float tx = l + 0.5f;
+		tx = tx >= 0 ? ( tx < (float)sf->lightextents[1] ? tx : (float)sf->lightextents[1] ) : 0;
+		tx = l - tx;
+		if( sx * sx + tx * tx + dist_sq >= maxdist )
+			continue;
+		out |= 1u << dl->bit;
+	}
+	bits[s] = out;
+}
 
 /* ---------------------------------------------------------------------------------------------- */
 /* display tail: R_BlitScreen (ref/soft/r_glblit.c:591-721) - every pixel_t goes through the 65536-entry
@@ -409,6 +488,11 @@ struct Dev
 	void *d_work[20] = {};
 	bool have_batch = false;
 	void *d_flush = nullptr;
+
+	/* dynamic lights of the next batch */
+	rc_dlight_t *d_dlights = nullptr;
+	uint32_t *d_dlightbits = nullptr;
+	int ndlights = 0;
 
 	/* display tail */
 	uint32_t *d_screenmap = nullptr;
@@ -542,6 +626,7 @@ rc_work_t make_slice( int k, int v0, int v1 )
 	ws.cache_list = D.d_list + (size_t)k * nslots;
 	ws.cache_nlist = D.d_nlist + 4 * k; ws.cache_cursor = ws.cache_nlist + 1; ws.line_cursor = ws.cache_nlist + 2;
 	ws.styles = D.d_styles; ws.counters = D.d_counters;
+	ws.dlights = D.d_dlights; ws.dlightbits = D.d_dlightbits; ws.ndlights = D.ndlights;
 	return ws;
 }
 
@@ -673,6 +758,9 @@ void rc_dev_shutdown( void )
 	free_batch();
 	if( D.d_display ) { cudaFree( D.d_display ); D.d_display = nullptr; D.display_bytes = 0; }
 	if( D.d_screenmap ) { cudaFree( D.d_screenmap ); D.d_screenmap = nullptr; }
+	if( D.d_dlights ) { cudaFree( D.d_dlights ); D.d_dlights = nullptr; }
+	if( D.d_dlightbits ) { cudaFree( D.d_dlightbits ); D.d_dlightbits = nullptr; }
+	D.ndlights = 0;
 	D.ready = false;
 }
 
@@ -793,6 +881,8 @@ int rc_dev_upload_scene( const rc_scene_t *sc, size_t cache_texels )
 
 	size_t nslots = (size_t)sc->numsurfaces * 4;
 	if( upload( &D.d_keys, (const rc_cachekey_t *)nullptr, nslots ) != 0 ) return -1;
+	if( upload( &D.d_dlightbits, (const uint32_t *)nullptr, (size_t)sc->numsurfaces + 1 ) != 0 ) return -1;
+	D.ndlights = 0;
 	if( upload( &D.d_need, (const uint32_t *)nullptr, RC_MAX_SLICES * ( nslots / 32 + 2 )) != 0 ) return -1;
 	if( upload( &D.d_list, (const int32_t *)nullptr, RC_MAX_SLICES * nslots ) != 0 ) return -1;
 	return 0;
@@ -814,6 +904,25 @@ int rc_dev_set_lightstyles( const int32_t *values )
 	memcpy( D.h_styles, values, sizeof( D.h_styles ));
 	CK( cudaStreamSynchronize( D.stream ));
 	CK( cudaMemcpy( D.d_styles, D.h_styles, sizeof( D.h_styles ), cudaMemcpyHostToDevice ));
+	return 0;
+}
+
+int rc_dev_set_dlights( const rc_dlight_t *lights, int n )
+{
+	if( n < 0 || n > RC_MAX_DLIGHTS ) return -1;
+	if( !n )
+	{
+		D.ndlights = 0;
+		return 0;
+	}
+	if( !D.sc.numsurfaces ) { snprintf( D.err, sizeof( D.err ), "rc_dev_set_dlights: no world" ); return -1; }
+	CK( cudaStreamSynchronize( D.stream ));
+	if( !D.d_dlights && dalloc( &D.d_dlights, RC_MAX_DLIGHTS ) != 0 ) return -1;
+	CK( cudaMemcpyAsync( D.d_dlights, lights, sizeof( rc_dlight_t ) * n, cudaMemcpyHostToDevice, D.stream ));
+	k_dlight_mark<<<( D.sc.numsurfaces + 127 ) / 128, 128, 0, D.stream>>>( D.sc, D.d_dlights, n, D.d_dlightbits );
+	D.launches++;
+	CK( cudaGetLastError());
+	D.ndlights = n;
 	return 0;
 }
 
@@ -903,7 +1012,7 @@ int rc_dev_read_cache_block( int surf, int mip, uint16_t *out, int maxtexels, in
 	if( sf->cache_ofs[mip] < 0 ) return 0;
 	rc_cachekey_t k;
 	CK( cudaMemcpy( &k, D.d_keys + surf * 4 + mip, sizeof( k ), cudaMemcpyDeviceToHost ));
-	bool stale = !k.valid || k.texnum != sf->texnum;
+	bool stale = !k.valid || k.texnum != sf->texnum; /* a block built with dynamic lights is a valid picture of the last batch */
 	for( int j = 0; j < 4 && sf->styles[j] != 255 && !stale; j++ )
 		if( k.light[j] != D.h_styles[sf->styles[j]] ) stale = true;
 	*valid = !stale;

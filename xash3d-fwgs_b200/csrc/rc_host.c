@@ -52,6 +52,8 @@ static CVAR_DEFINE_AUTO( sw_mipscale, "1", FCVAR_GLCONFIG, "nothing" );
 static CVAR_DEFINE_AUTO( sw_noalphabrushes, "0", FCVAR_GLCONFIG, "" );
 static CVAR_DEFINE_AUTO( cu_device, "0", FCVAR_GLCONFIG, "CUDA device ordinal used by ref_cuda" );
 static CVAR_DEFINE_AUTO( r_novis, "0", 0, "" );
+/* ref/common/ref_light.c:21 */
+static CVAR_DEFINE_AUTO( r_dlight_virtual_radius, "3", FCVAR_GLCONFIG, "increase dlight radius virtually by this amount" );
 
 /* ---------------------------------------------------------------------------------------------- */
 /* texture table (image_t of ref/soft/r_local.h:287-312, host mirror; texels are uploaded as one arena) */
@@ -90,6 +92,7 @@ static struct
 	int          nviews, maxviews;
 
 	void        *swbuffer_info_valid;
+	int          had_dlights;
 	uint         sw_stride, sw_bpp, sw_r, sw_g, sw_b;
 	uint         map_valid, map_bpp, map_r, map_g, map_b; /* display format the device's screen map was built for */
 	char         error[512];
@@ -758,6 +761,32 @@ static void rc_setup_view( const ref_viewpass_t *rvp, rc_view_t *v )
 /* ---------------------------------------------------------------------------------------------- */
 /* frames: views queue up between R_BeginFrame and R_EndFrame and are rendered as one batch          */
 
+/* R_PushDlights (ref/common/ref_light.c:170): the engine's dynamic lights that are alive at the frame's time; the
+ * faces each one reaches are marked on the device (k_dlight_mark), the light is added by k_cache_build */
+static void rc_push_dlights( void )
+{
+	const dlight_t *dl = (const dlight_t *)gEngfuncs.EngineGetParm( PARM_GET_DLIGHTS_PTR, 0 );
+	rc_dlight_t act[RC_MAX_DLIGHTS];
+	int n = 0;
+	for( int i = 0; dl && i < MAX_DLIGHTS && i < RC_MAX_DLIGHTS; i++ )
+	{
+		const dlight_t *l = &dl[i];
+		if( l->die < gp_cl->time || !l->radius )
+			continue;
+		rc_dlight_t *o = &act[n++];
+		VectorCopy( l->origin, o->origin );
+		o->radius = l->radius;
+		o->minlight = l->minlight;
+		uint b = ( l->color.r + l->color.g + l->color.b ) / 3 * 4;
+		o->monolight = (int)(( b >= 1024 ? 0u : (uint)rc.lightgamma[b] ) * 3 );
+		o->bit = i;
+		o->virtual_radius = l->radius * Q_max( 1.0f, r_dlight_virtual_radius.value );
+	}
+	if( n || rc.had_dlights )
+		RC_CHECK_DEV( rc_dev_set_dlights( act, n ));
+	rc.had_dlights = n > 0;
+}
+
 static void rc_prepare_batch( void )
 {
 	if( !rc.scene_valid )
@@ -765,6 +794,7 @@ static void rc_prepare_batch( void )
 	rc_sync_textures();
 	rc_resolve_texnums( false );
 	RC_CHECK_DEV( rc_dev_set_lightstyles( rc.lightstylevalue ));
+	rc_push_dlights();
 }
 
 static void rc_queue_view( const ref_viewpass_t *rvp )
@@ -923,6 +953,7 @@ static qboolean R_Init( void )
 	gEngfuncs.Cvar_RegisterVariable( &sw_noalphabrushes );
 	gEngfuncs.Cvar_RegisterVariable( &cu_device );
 	gEngfuncs.Cvar_RegisterVariable( &r_novis );
+	gEngfuncs.Cvar_RegisterVariable( &r_dlight_virtual_radius );
 
 	rc.pool = gEngfuncs._Mem_AllocPool( "ref_cuda zone", 0, __FILE__, __LINE__ );
 

@@ -113,6 +113,18 @@ typedef struct
 	                                * instead of the surfedges -> edges -> verts chain of three dependent ones */
 } rc_scene_t;
 
+/* an active dynamic light of the batch (dlight_t, common/q_client.h:57, after R_PushDlights' die / radius test) */
+#define RC_MAX_DLIGHTS 32
+typedef struct
+{
+	float   origin[3];
+	float   radius;
+	float   minlight;
+	int32_t monolight; /* LightToTexGamma(( r + g + b ) / 3 * 4 ) * 3, ref/soft/r_surf.c:138 */
+	int32_t bit;       /* index in the engine's table = bit in msurface_t.dlightbits */
+	float   virtual_radius; /* radius * max( 1, r_dlight_virtual_radius ), ref/common/ref_light.c:96 */
+} rc_dlight_t; /* 32 B */
+
 /* per-view constants: everything R_SetupFrustum/R_SetupFrameQ/R_ViewChanged/R_TransformFrustum derive
  * (ref/soft/r_main.c:387, r_misc.c:101-322).  Computed on the host with the host libm and the reference's
  * float expression order, so the device never re-derives a transcendental. */

@@ -77,6 +77,14 @@ class Renderer:
     def set_lightstyle(self, i, pattern, time=0.0):
         self.host.set_lightstyle(i, pattern, time)
 
+    def set_dlight(self, i, origin, radius, color=(255, 255, 255), die=1e9, minlight=0.0):
+        """Entry i of the engine's dynamic light table (dlight_t); radius 0 switches it off."""
+        L = self.host.lib
+        L.xh_set_dlight.argtypes = [C.c_int, C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float]
+        o = (C.c_float * 3)(*[float(x) for x in origin])
+        if L.xh_set_dlight(i, o, float(radius), int(color[0]), int(color[1]), int(color[2]), float(die), float(minlight)) != 0:
+            raise ValueError("dlight index out of range")
+
     def run_lightstyles(self):
         self.host.run_lightstyles()
 
