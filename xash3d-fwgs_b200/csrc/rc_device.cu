@@ -55,7 +55,8 @@ struct rc_work_t
 	rc_cachekey_t *cache_keys; /* [numsurfaces * 4] */
 	int32_t   *cache_list;/* [numsurfaces * 4] work list of surf * 4 + mip */
 	int32_t   *cache_nlist, *cache_cursor;
-	int32_t   *line_cursor; /* k_lines work cursor */
+	int32_t   *line_cursor; /* k_lines work cursors: heavy list, all lines */
+	int32_t   *heavy_list, *heavy_count; /* [nviews * height] lines with more than LN_HEAVY events (k_events), their number */
 	const int32_t *styles;/* [256] g_lightstylevalue */
 	const rc_dlight_t *dlights; /* active dynamic lights of the batch */
 	const uint32_t *dlightbits; /* [numsurfaces] msurface_t.dlightbits (k_dlight_mark) */
@@ -590,6 +591,7 @@ int ensure_batch( int nviews, int width, int height )
 	WALLOC( bandnloc, int32_t, (size_t)cap * w.nbands );
 	WALLOC( events, unsigned long long, (size_t)cap * w.view_events );
 	WALLOC( lineinfo, rc_lineinfo_t, (size_t)cap * height );
+	WALLOC( heavy_list, int32_t, (size_t)cap * height );
 	WALLOC( color, uint16_t, (size_t)cap * width * height );
 	WALLOC( zbuf, int16_t, (size_t)cap * width * height );
 #undef WALLOC
@@ -624,7 +626,8 @@ rc_work_t make_slice( int k, int v0, int v1 )
 	ws.cache_need = D.d_need + (size_t)k * ( nslots / 32 + 2 );
 	ws.cache_keys = D.d_keys;
 	ws.cache_list = D.d_list + (size_t)k * nslots;
-	ws.cache_nlist = D.d_nlist + 4 * k; ws.cache_cursor = ws.cache_nlist + 1; ws.line_cursor = ws.cache_nlist + 2;
+	ws.cache_nlist = D.d_nlist + 8 * k; ws.cache_cursor = ws.cache_nlist + 1; ws.line_cursor = ws.cache_nlist + 2; ws.heavy_count = ws.cache_nlist + 4;
+	ws.heavy_list += (size_t)v0 * ws.height;
 	ws.styles = D.d_styles; ws.counters = D.d_counters;
 	ws.dlights = D.d_dlights; ws.dlightbits = D.d_dlightbits; ws.ndlights = D.ndlights;
 	return ws;
@@ -635,7 +638,7 @@ int launch_slice( const rc_work_t &ws, cudaStream_t st, cudaEvent_t *evs, bool d
 {
 	const rc_scene_t &sc = D.sc;
 	CK( cudaMemsetAsync( ws.cache_need, 0, sizeof( uint32_t ) * (( sc.numsurfaces * 4 + 31 ) / 32 + 1 ), st ));
-	CK( cudaMemsetAsync( ws.cache_nlist, 0, sizeof( int32_t ) * 4, st ));
+	CK( cudaMemsetAsync( ws.cache_nlist, 0, sizeof( int32_t ) * 8, st ));
 	if( evs ) CK( cudaEventRecord( evs[0], st ));
 	k_viswalk<VW_NTHREADS><<<ws.nviews, VW_NTHREADS, (size_t)ws.vis_smem, st>>>( sc, ws );
 	D.launches++;
@@ -746,7 +749,7 @@ int rc_dev_init( int device )
 	if( upload( &D.d_styles, D.h_styles, 256 ) != 0 ) return -1;
 	if( dalloc( &D.d_counters, RC_CTR_COUNT ) != 0 ) return -1;
 	CK( cudaMemset( D.d_counters, 0, sizeof( unsigned long long ) * RC_CTR_COUNT ));
-	if( dalloc( &D.d_nlist, 4 * RC_MAX_SLICES ) != 0 ) return -1;
+	if( dalloc( &D.d_nlist, 8 * RC_MAX_SLICES ) != 0 ) return -1;
 	D.ready = true;
 	return 0;
 }

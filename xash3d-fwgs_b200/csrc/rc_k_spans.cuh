@@ -23,7 +23,7 @@
 #define EV_THREADS  256
 #define EV_WARPS    ( EV_THREADS / 32 )
 #define LN_WARPS    4
-#define LN_HEAVY    64   /* events: lines above go first */
+#define LN_HEAVY    128  /* events: lines above are listed by k_events and go first (measured: 32: 166 us, 64: 159, 128: 153, 192: 159) */
 #define LN_CHUNK    1    /* scanlines a warp takes from the shared cursor at a time (measured on the C2 batch: 1: 170 us, 2: 172, 4: 183, 8: 184) */
 #define SP_SORTCAP  512  /* events per line the shared-memory sorter takes; longer lines fall back to a serial sort */
 #define SP_BITWORDS 64   /* shared-memory bit-set words per line (views listing <= 2015 faces), else global scratch */
@@ -256,6 +256,7 @@ __global__ void __launch_bounds__( EV_THREADS ) k_events( rc_work_t w )
 		{
 			li.ofs = band * w.blk_events + off; /* index inside the view's arena */
 			li.nsp = n;                         /* events for now; k_lines replaces it with the span count */
+			if( n > LN_HEAVY ) w.heavy_list[atomicAdd( w.heavy_count, 1 )] = view * w.height + y;
 		}
 		else if( valid )
 			atomicAdd( &w.counters[RC_CTR_OVERFLOW_EVENTS], 1ull );
@@ -443,33 +444,36 @@ __global__ void __launch_bounds__( LN_WARPS * 32, 8 ) k_lines( rc_work_t w )
 	/* scanlines differ a lot in cost (2 .. 500 events) and the heavy ones cluster (the horizon of corridor views):
 	 * warps draw them from a shared cursor, view-interleaved */
 	/* two sweeps over the lines: the heavy ones first (longest processing time first keeps the tail short) */
-	const int32_t chunk = LN_CHUNK;
-	for( int32_t q = 0, heavy = 1; ; q++ )
+	const int32_t nheavy = *w.heavy_count; /* k_events listed the lines with more than LN_HEAVY events */
+	for( int32_t heavy = 1; ; )
 	{
 		int32_t item = 0;
-		if(( q & ( chunk - 1 )) == 0 )
-		{
-			if( lane == 0 ) item = atomicAdd( w.line_cursor + ( heavy ? 0 : 1 ), chunk );
-			cur = __shfl_sync( 0xFFFFFFFFu, item, 0 );
-		}
-		item = cur + ( q & ( chunk - 1 ));
-		if( cur >= nlines )
+		if( lane == 0 ) item = atomicAdd( w.line_cursor + ( heavy ? 0 : 1 ), 1 );
+		item = __shfl_sync( 0xFFFFFFFFu, item, 0 );
+		if( item >= ( heavy ? nheavy : nlines ))
 		{
 			if( !heavy )
 				break;
-			heavy = 0; q = -1;
+			heavy = 0;
 			continue;
 		}
-		if( item >= nlines )
-			continue;
-		const int32_t view = item % w.nviews;
-		const int32_t line = view * w.height + item / w.nviews;
+		int32_t view, line;
+		if( heavy )
+		{
+			line = w.heavy_list[item];
+			view = line / w.height;
+		}
+		else
+		{
+			view = item % w.nviews;
+			line = view * w.height + item / w.nviews;
+		}
 		const rc_lineinfo_t li = w.lineinfo[line];
 		if( li.ofs < 0 )
 			continue;
 		const int32_t n = li.nsp;
-		if(( n & RC_LINE_DONE ) || ( n > LN_HEAVY ) != ( heavy != 0 ))
-			continue; /* done in the first sweep, or the other sweep's line */
+		if(( n & RC_LINE_DONE ) || ( !heavy && n > LN_HEAVY ))
+			continue; /* done in the first sweep */
 		const rc_view_t *vw = &w.views[view];
 		const int32_t x0 = vw->vrect[0], vw_w = vw->vrect[2];
 #ifdef RC_SPANS_DEBUG
