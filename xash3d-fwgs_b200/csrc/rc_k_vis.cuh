@@ -427,21 +427,20 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 	const int32_t nseq = nlvl ? e_size[0] : 0;
 	for( int32_t i = t; i < nseq; i += VW_THREADS ) seq[i] = 0;
 	__syncthreads();
-	for( int32_t wi = t; wi < w.surfwords; wi += VW_THREADS )
+	/* thread per surface (a word of the mark set per thread would leave most of the block idle and walk up to 32
+	 * bits serially); a thread only ever changes its own bit */
+	for( int32_t s = t; s < sc.numsurfaces; s += VW_THREADS )
 	{
-		uint32_t m = surfmark[wi];
-		while( m )
-		{
-			const int32_t s = ( wi << 5 ) + __ffs( (int)m ) - 1;
-			m &= m - 1;
-			const int32_t n = sn16 ? (int32_t)sn16[s] : sc.surfnode[s];
-			const int want = ( nflag[n] >> 9 ) & 3; /* 2: the eye is on the plane, nothing is posted */
-			const int back = ( sc.surfback[wi] >> ( s & 31 )) & 1;
-			if( back == want )
-				atomicAdd( &seq[nodepos[n]], 1 );
-			else
-				atomicAnd( &surfmark[wi], ~( 1u << ( s & 31 ))); /* marked but facing away: not a candidate */
-		}
+		const int32_t wi = s >> 5;
+		if( !(( surfmark[wi] >> ( s & 31 )) & 1 ))
+			continue;
+		const int32_t n = sn16 ? (int32_t)sn16[s] : sc.surfnode[s];
+		const int want = ( nflag[n] >> 9 ) & 3; /* 2: the eye is on the plane, nothing is posted */
+		const int back = ( sc.surfback[wi] >> ( s & 31 )) & 1;
+		if( back == want )
+			atomicAdd( &seq[nodepos[n]], 1 );
+		else
+			atomicAnd( &surfmark[wi], ~( 1u << ( s & 31 ))); /* marked but facing away: not a candidate */
 	}
 	__syncthreads();
 	int32_t carry = 0;
@@ -464,30 +463,27 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 	}
 	const int32_t total = carry;
 	rc_cand_t *cands = w.cands + (size_t)view * w.max_cands;
-	for( int32_t wi = t; wi < w.surfwords; wi += VW_THREADS )
+	for( int32_t s = t; s < sc.numsurfaces; s += VW_THREADS )
 	{
-		uint32_t m = surfmark[wi];
-		while( m )
+		const int32_t wi = s >> 5, b = s & 31;
+		if( !(( surfmark[wi] >> b ) & 1 ))
+			continue;
+		const int32_t n = sn16 ? (int32_t)sn16[s] : sc.surfnode[s], pos = nodepos[n];
+		/* rank among the node's candidates: surviving marks in [firstsurface, s) */
+		const int32_t f = sc.nodes[n].firstsurface;
+		int32_t rank = 0;
+		for( int32_t k = f >> 5; k <= wi; k++ )
 		{
-			const int32_t b = __ffs( (int)m ) - 1, s = ( wi << 5 ) + b;
-			m &= m - 1;
-			const int32_t n = sn16 ? (int32_t)sn16[s] : sc.surfnode[s], pos = nodepos[n];
-			/* rank among the node's candidates: surviving marks in [firstsurface, s) */
-			const int32_t f = sc.nodes[n].firstsurface;
-			int32_t rank = 0;
-			for( int32_t k = f >> 5; k <= wi; k++ )
-			{
-				uint32_t mk = surfmark[k];
-				if( k == ( f >> 5 )) mk &= ~0u << ( f & 31 );
-				if( k == wi ) mk &= ( 1u << b ) - 1u;
-				rank += __popc( mk );
-			}
-			const int32_t o = seq[pos] + rank;
-			if( o < w.max_cands )
-			{
-				cands[o].surf = s;
-				cands[o].clipflags = posclip[pos];
-			}
+			uint32_t mk = surfmark[k];
+			if( k == ( f >> 5 )) mk &= ~0u << ( f & 31 );
+			if( k == wi ) mk &= ( 1u << b ) - 1u;
+			rank += __popc( mk );
+		}
+		const int32_t o = seq[pos] + rank;
+		if( o < w.max_cands )
+		{
+			cands[o].surf = s;
+			cands[o].clipflags = posclip[pos];
 		}
 	}
 
