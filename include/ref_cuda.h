@@ -53,7 +53,8 @@ REF_CUDA_EXPORT int RefCuda_BlitViews( int first, int nviews, void *dst, unsigne
  * per iteration: total and per stage, ms_stage[5] = [visibility+BSP walk, face/edge set-up, surface cache,
  * span generation, span drawing].
  * flags: 1 = invalidate the surface cache before every iteration, 2 = flush L2 (256 MB write) between
- * iterations, outside the timed region. */
+ * iterations, outside the timed region, 8 = run the surface-cache kernels on the batch's stream instead of beside span
+ * generation (times them alone; by default ms_stage[2] overlaps ms_stage[3]). */
 REF_CUDA_EXPORT int RefCuda_BenchResident( int iters, int flags, float *ms_total, float *ms_stage );
 
 /* Surface cache block of (surface, mip) as built on the device (D_CacheSurface, ref/soft/r_surf.c:1053). */

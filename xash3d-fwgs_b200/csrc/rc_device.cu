@@ -460,6 +460,9 @@ struct Dev
 	cudaStream_t stream = nullptr, copy = nullptr;
 	cudaStream_t slice_stream[RC_MAX_SLICES] = {};
 	cudaEvent_t ev_slice[RC_MAX_SLICES] = {}, ev_fork = nullptr;
+	cudaStream_t aux_stream[RC_MAX_SLICES] = {};           /* surface-cache kernels of a slice, beside its span kernels */
+	cudaEvent_t ev_cache[RC_MAX_SLICES][2] = {};           /* start / end of those */
+	bool cache_aside = true;                               /* false: on the slice's own stream (the bench times the kernels alone) */
 	cudaEvent_t ev[8] = {};
 	uint64_t launches = 0;
 
@@ -634,7 +637,7 @@ rc_work_t make_slice( int k, int v0, int v1 )
 }
 
 /* all stages of one slice on stream st; evs != NULL: stage boundaries are recorded there */
-int launch_slice( const rc_work_t &ws, cudaStream_t st, cudaEvent_t *evs, bool draw )
+int launch_slice( const rc_work_t &ws, int k, cudaStream_t st, cudaEvent_t *evs, bool draw )
 {
 	const rc_scene_t &sc = D.sc;
 	CK( cudaMemsetAsync( ws.cache_need, 0, sizeof( uint32_t ) * (( sc.numsurfaces * 4 + 31 ) / 32 + 1 ), st ));
@@ -651,9 +654,14 @@ int launch_slice( const rc_work_t &ws, cudaStream_t st, cudaEvent_t *evs, bool d
 	}
 	if( evs ) CK( cudaEventRecord( evs[2], st ));
 	{
+		/* the surface cache is only read by k_draw: its kernels run on a side stream, beside span generation */
+		cudaStream_t aux = D.cache_aside ? D.aux_stream[k] : st;
+		CK( cudaEventRecord( D.ev_cache[k][0], st ));
+		if( D.cache_aside ) CK( cudaStreamWaitEvent( aux, D.ev_cache[k][0], 0 ));
 		int nslots = sc.numsurfaces * 4;
-		k_cache_list<<<( nslots + 255 ) / 256, 256, 0, st>>>( sc, ws ); D.launches++;
-		k_cache_build<<<148 * 4, CACHE_THREADS, 0, st>>>( sc, ws ); D.launches++;
+		k_cache_list<<<( nslots + 255 ) / 256, 256, 0, aux>>>( sc, ws ); D.launches++;
+		k_cache_build<<<148 * 4, CACHE_THREADS, 0, aux>>>( sc, ws ); D.launches++;
+		CK( cudaEventRecord( D.ev_cache[k][1], aux ));
 	}
 	if( evs ) CK( cudaEventRecord( evs[3], st ));
 	const int nlines = ws.nviews * ws.height;
@@ -664,6 +672,7 @@ int launch_slice( const rc_work_t &ws, cudaStream_t st, cudaEvent_t *evs, bool d
 		k_lines<<<lblocks < LN_GRID ? lblocks : LN_GRID, LN_WARPS * 32, 0, st>>>( ws ); D.launches++;
 	}
 	if( evs ) CK( cudaEventRecord( evs[4], st ));
+	if( D.cache_aside ) CK( cudaStreamWaitEvent( st, D.ev_cache[k][1], 0 ));
 	if( draw )
 	{
 		const int lpw = rc_draw_lpw( ws.width, ws.height );
@@ -689,7 +698,7 @@ int run_batch( int nslices, int nstreams, bool timed, uint16_t *color_out, int16
 	if( nslices <= 1 )
 	{
 		const rc_work_t ws = make_slice( 0, 0, w.nviews );
-		if( launch_slice( ws, st, timed ? D.ev : nullptr, true ) != 0 ) return -1;
+		if( launch_slice( ws, 0, st, timed ? D.ev : nullptr, true ) != 0 ) return -1;
 		if( color_out ) CK( cudaMemcpyAsync( color_out, w.color, (size_t)w.nviews * vpx * 2, cudaMemcpyDeviceToHost, st ));
 		if( z_out ) CK( cudaMemcpyAsync( z_out, w.zbuf, (size_t)w.nviews * vpx * 2, cudaMemcpyDeviceToHost, st ));
 		CK( cudaGetLastError());
@@ -703,7 +712,7 @@ int run_batch( int nslices, int nstreams, bool timed, uint16_t *color_out, int16
 		const int v0 = (int)((long long)w.nviews * k / nslices ), v1 = (int)((long long)w.nviews * ( k + 1 ) / nslices );
 		cudaStream_t ss = D.slice_stream[k % nstreams];
 		const rc_work_t ws = make_slice( k, v0, v1 );
-		if( launch_slice( ws, ss, nullptr, true ) != 0 ) return -1;
+		if( launch_slice( ws, k, ss, nullptr, true ) != 0 ) return -1;
 		CK( cudaEventRecord( D.ev_slice[k], ss ));
 		if( color_out || z_out )
 		{
@@ -741,6 +750,8 @@ int rc_dev_init( int device )
 	for( auto &e : D.ev_slice ) CK( cudaEventCreateWithFlags( &e, cudaEventDisableTiming ));
 	CK( cudaEventCreateWithFlags( &D.ev_fork, cudaEventDisableTiming ));
 	for( auto &ss : D.slice_stream ) CK( cudaStreamCreateWithFlags( &ss, cudaStreamNonBlocking ));
+	for( auto &ss : D.aux_stream ) CK( cudaStreamCreateWithFlags( &ss, cudaStreamNonBlocking ));
+	for( auto &e : D.ev_cache ) { CK( cudaEventCreate( &e[0] )); CK( cudaEventCreate( &e[1] )); }
 	for( auto &e : D.ev ) CK( cudaEventCreate( &e ));
 	CK( cudaFuncSetAttribute( k_viswalk<VW_NTHREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 64 ));
 	CK( cudaFuncSetAttribute( k_events, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_events_smem( EV_ECAP_BIG, 65536 / 32 + 2 )));
@@ -985,6 +996,7 @@ int rc_dev_bench_resident( int iters, int flags, float *ms_total, float *ms_stag
 	const size_t flush_bytes = (size_t)256 << 20; /* > 126 MB of L2 */
 	if(( flags & RC_BENCH_FLUSH_L2 ) && !D.d_flush )
 		CK( cudaMalloc( &D.d_flush, flush_bytes ));
+	D.cache_aside = !( flags & RC_BENCH_SERIAL_CACHE );
 	for( int it = 0; it < iters; it++ )
 	{
 		if( flags & RC_BENCH_FLUSH_L2 ) /* untimed: the events bracket the stages only */
@@ -993,14 +1005,20 @@ int rc_dev_bench_resident( int iters, int flags, float *ms_total, float *ms_stag
 			CK( cudaMemsetAsync( D.d_keys, 0, sizeof( rc_cachekey_t ) * (size_t)D.sc.numsurfaces * 4, D.stream ));
 		{
 			const bool overlap = ( flags & RC_BENCH_OVERLAP ) && D.w.nviews >= 16 * RC_MAX_SLICES;
-			if( run_batch( overlap ? RC_MAX_SLICES : 1, 2, true, nullptr, nullptr ) != 0 ) return -1;
+			if( run_batch( overlap ? RC_MAX_SLICES : 1, 2, true, nullptr, nullptr ) != 0 ) { D.cache_aside = true; return -1; }
 			if( overlap ) overlapped = true;
 		}
 		CK( cudaStreamSynchronize( D.stream ));
 		float ms;
 		CK( cudaEventElapsedTime( &ms, D.ev[0], D.ev[RC_BENCH_STAGES] )); tot += ms;
-		if( !overlapped ) for( int s = 0; s < RC_BENCH_STAGES; s++ ) { CK( cudaEventElapsedTime( &ms, D.ev[s], D.ev[s + 1] )); stage[s] += ms; }
+		if( !overlapped )
+		{
+			for( int s = 0; s < RC_BENCH_STAGES; s++ ) { CK( cudaEventElapsedTime( &ms, D.ev[s], D.ev[s + 1] )); stage[s] += ms; }
+			/* the cache kernels run beside span generation: their own events (the stream's events see nothing of them) */
+			if( D.cache_aside ) { CK( cudaEventElapsedTime( &ms, D.ev_cache[0][0], D.ev_cache[0][1] )); stage[2] += ms; }
+		}
 	}
+	D.cache_aside = true;
 	if( ms_total ) *ms_total = tot / ( iters > 0 ? iters : 1 );
 	if( ms_stage ) for( int s = 0; s < RC_BENCH_STAGES; s++ ) ms_stage[s] = stage[s] / ( iters > 0 ? iters : 1 );
 	return 0;

@@ -179,13 +179,13 @@ class Renderer:
         if self._render(C.addressof(vp), len(vp), color_ptr, z_ptr, 1 if clear else 0) != 0:
             raise RuntimeError("RefCuda_RenderViews failed")
 
-    def bench_resident(self, iters, rebuild_cache=False, flush_l2=False, overlap=False):
+    def bench_resident(self, iters, rebuild_cache=False, flush_l2=False, overlap=False, serial_cache=False):
         """CUDA-event ms per iteration of the last batch re-run with inputs resident in HBM: (total, [5 stages: vis_walk,
         faces_edges, surface_cache, spans, draw]).  overlap=True: the slicing RefCuda_RenderViews uses for host outputs (4 view
         slices on 2 streams): total only, the stage list is zeros."""
         tot = C.c_float()
         st = (C.c_float * 5)()
-        if self._bench(iters, (1 if rebuild_cache else 0) | (2 if flush_l2 else 0) | (4 if overlap else 0), C.byref(tot), st) != 0:
+        if self._bench(iters, (1 if rebuild_cache else 0) | (2 if flush_l2 else 0) | (4 if overlap else 0) | (8 if serial_cache else 0), C.byref(tot), st) != 0:
             raise RuntimeError("RefCuda_BenchResident failed")
         return tot.value, list(st)
 
