@@ -3,12 +3,14 @@
  * code calls.  One batch = N independent camera views of one world at one timestamp.
  *
  * Stage map (reference function -> kernel), all per batch:
- *   S0 k_viswalk      Mod_PointInLeaf/Mod_FatPVS/R_MarkLeaves + R_RecursiveWorldNode   one warp per view
+ *   S0 k_viswalk      Mod_PointInLeaf/Mod_FatPVS/R_MarkLeaves + R_RecursiveWorldNode   one block per view (rc_k_vis.cuh)
  *   S1 k_faces        R_RenderFace/R_ClipEdge/R_EmitEdge + D_CalcGradients             one thread per (view, face)
  *   S2 k_cache_list   D_CacheSurface staleness test -> work list                        one thread per (face, mip)
- *      k_cache_build  R_BuildLightMap + R_DrawSurface                                   persistent CTAs, one block per (face, mip)
+ *      k_cache_build  R_BuildLightMap (+ R_AddDynamicLights) + R_DrawSurface            persistent CTAs, one block per (face, mip)
+ *      k_dlight_mark  R_PushDlights/R_MarkLights                                        one thread per face, once per light set
  *   S3 k_events/k_lines R_ScanEdges/R_GenerateSpans (rc_k_spans.cuh)                    lane per scanline / warp per scanline
- *      k_draw         D_DrawSpans16/D_DrawZSpans/Turbulent8/D_BackgroundSurf (rc_k_draw.cuh) one warp per (view, scanline)
+ *      k_draw         D_DrawSpans16/D_DrawZSpans/Turbulent8/D_BackgroundSurf (rc_k_draw.cuh) one warp per group of scanlines
+ *   S4 k_blit         R_BlitScreen with the R_BuildScreenMap table                      one thread per 8 pixels
  *
  * The per-item arithmetic is rc_core.h (shared with the CPU debug harness); this file is the parallel
  * decomposition, the memory layout and the stream plumbing.  Compiled with -fmad=false and IEEE

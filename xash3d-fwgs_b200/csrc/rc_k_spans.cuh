@@ -6,20 +6,22 @@
  * closed form (u0 + (y - v) * u_step in int32 wraparound, r_edge.c:187), so scanlines are independent given
  * the edge set.  Two kernels:
  *
- *   k_events  block per (view, band of SP_LINES = 32 scanlines), lane = scanline, warps stride over the band's
- *             edge list (binned by k_faces): pass 1 counts the edges crossing every line in registers, a block
- *             prefix sum gives every line its slice of the band's arena in HBM, pass 2 writes the event keys
- *             {u at the line, surfaces}.  No atomics.
- *   k_lines   warp per scanline, lines strided over the whole grid so that the heavy lines of one view land on
- *             different SMs: load the line's keys (coalesced), bitonic sort (registers + shuffles up to 32 events,
- *             shared memory up to SP_SORTCAP) = the order R_InsertNewEdges / R_StepActiveU keep incrementally,
- *             then replay them against the surface bit set (rc_generate_spans_bits) out of shared memory; the spans
- *             overwrite the slice, the count goes to the line table k_draw reads.
+ *   k_events  block per (view, band of SP_LINES = 32 scanlines), bands issued from the middle of the frame outwards:
+ *             gathers the view's edges that cross the band (ballot compaction), pre-sorts them by u at the band's
+ *             middle line, renumbers the band's surfaces locally, permutes the edges into sorted order; then lane =
+ *             scanline, warps take runs of the sorted list: pass 1 counts the edges crossing every line, a prefix sum
+ *             gives every line its slice of the band's arena in HBM, pass 2 writes the event keys {u at the line,
+ *             band-local surfaces} - nearly sorted already.  Lines with more than LN_HEAVY events go to a list.
+ *   k_lines   warp per scanline, lines drawn from shared cursors (the heavy list first): sortedness check, odd-even
+ *             passes / bitonic network (registers + shuffles up to 32 events, shared memory up to SP_SORTCAP) = the
+ *             order R_InsertNewEdges / R_StepActiveU keep incrementally, then the replay against the surface bit set
+ *             by the whole warp (rc_replay_warp: XOR scan, 32 events per round; rc_generate_spans_bits for degenerate
+ *             lines); the spans overwrite the slice, the count goes to the line table k_draw reads.
  */
 #ifndef RC_K_SPANS_CUH
 #define RC_K_SPANS_CUH
 
-/* SP_LINES (scanlines per band) is defined by rc_device.cu: k_faces bins edges by band */
+/* SP_LINES (scanlines per band) is defined by rc_device.cu */
 #define EV_THREADS  256
 #define EV_WARPS    ( EV_THREADS / 32 )
 #define LN_WARPS    4
