@@ -332,3 +332,17 @@ def test_dynamic_lights_match_reference(pkg, scene):
     off_c, _ = so.render_views(cams)
     got_c, _ = cu.render_views(cams)
     assert np.array_equal(off_c, base_c) and np.array_equal(got_c, base_c)
+
+
+@pytest.mark.gpu
+def test_renderer_restart_in_one_process(pkg, scene):
+    """R_Shutdown followed by R_Init (what vid_restart does): the device side frees everything and comes up again."""
+    m = scene.make_map("tiny", ncameras=16)
+    cu = scene.Renderer(pkg.REF_CUDA_PATH, 320, 240, m)
+    a, az = cu.render_views(m.cameras[:4])
+    L = cu.host.lib
+    assert L.xh_restart() == 0, L.xh_last_error().decode()
+    cu.load_map(m)
+    b, bz = cu.render_views(m.cameras[:4])
+    assert np.array_equal(a, b) and np.array_equal(az, bz)
+    assert cu.launch_count() > 0

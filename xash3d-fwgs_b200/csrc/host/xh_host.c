@@ -487,6 +487,15 @@ void xh_shutdown( void )
 	xh.dll = NULL;
 }
 
+/* R_Shutdown + R_Init on the loaded renderer (what the engine's vid_restart does); the map has to be loaded again */
+int xh_restart( void )
+{
+	if( !xh.dll )
+		return -1;
+	xh.ref.R_Shutdown();
+	return xh.ref.R_Init() ? 0 : -5;
+}
+
 void *xh_ref_symbol( const char *name ) { return xh.dll ? dlsym( xh.dll, name ) : NULL; }
 uint64_t xh_callback_count( void ) { return xh.callbacks; }
 

@@ -53,6 +53,9 @@ XH_EXPORT void xh_clear_scene( void );
 XH_EXPORT int xh_add_brush_entity( int modelindex, const float *origin, const float *angles,
 	int rendermode, int renderamt );
 
+/* R_Shutdown + R_Init on the loaded renderer (vid_restart); load the map again afterwards */
+XH_EXPORT int xh_restart( void );
+
 /* raw access for harnesses */
 XH_EXPORT void *xh_ref_symbol( const char *name );      /* dlsym on the renderer .so */
 XH_EXPORT void *xh_world_model( void );                  /* model_t* */

@@ -772,11 +772,24 @@ void rc_dev_shutdown( void )
 	if( !D.ready ) return;
 	cudaDeviceSynchronize();
 	free_batch();
-	if( D.d_display ) { cudaFree( D.d_display ); D.d_display = nullptr; D.display_bytes = 0; }
-	if( D.d_screenmap ) { cudaFree( D.d_screenmap ); D.d_screenmap = nullptr; }
-	if( D.d_dlights ) { cudaFree( D.d_dlights ); D.d_dlights = nullptr; }
-	if( D.d_dlightbits ) { cudaFree( D.d_dlightbits ); D.d_dlightbits = nullptr; }
-	D.ndlights = 0;
+	/* everything rc_dev_init / the uploads created, so that R_Shutdown + R_Init (vid_restart) starts clean */
+	void **ptrs[] = { (void **)&D.d_display, (void **)&D.d_screenmap, (void **)&D.d_dlights, (void **)&D.d_dlightbits,
+		(void **)&D.d_colormap, (void **)&D.d_lightgamma, (void **)&D.d_sintable, (void **)&D.d_textures, (void **)&D.d_texels,
+		(void **)&D.d_styles, (void **)&D.d_keys, (void **)&D.d_need, (void **)&D.d_list, (void **)&D.d_nlist,
+		(void **)&D.d_counters, &D.d_flush };
+	for( void **p : ptrs ) { if( *p ) cudaFree( *p ); *p = nullptr; }
+	for( void *&p : D.d_scene ) { if( p ) cudaFree( p ); p = nullptr; }
+	D.display_bytes = 0; D.ndlights = 0; D.screen_bpp = 0; D.cache_texels = 0; D.ntextures = 0;
+	D.sc = rc_scene_t{}; D.h_surfaces.clear(); D.h_textures.clear();
+	cudaStream_t *streams[] = { &D.stream, &D.copy };
+	for( cudaStream_t *st : streams ) { if( *st ) cudaStreamDestroy( *st ); *st = nullptr; }
+	for( auto &ss : D.slice_stream ) { if( ss ) cudaStreamDestroy( ss ); ss = nullptr; }
+	for( auto &ss : D.aux_stream ) { if( ss ) cudaStreamDestroy( ss ); ss = nullptr; }
+	for( auto &e : D.ev_slice ) { if( e ) cudaEventDestroy( e ); e = nullptr; }
+	for( auto &e : D.ev ) { if( e ) cudaEventDestroy( e ); e = nullptr; }
+	for( auto &e : D.ev_cache ) for( auto &x : e ) { if( x ) cudaEventDestroy( x ); x = nullptr; }
+	if( D.ev_fork ) { cudaEventDestroy( D.ev_fork ); D.ev_fork = nullptr; }
+	D.launches = 0;
 	D.ready = false;
 }
 

@@ -118,7 +118,7 @@ class Renderer:
             vp = self.viewpasses(cams, fov_x, flags, viewport)
             rc = self._render(C.addressof(vp), n, color.ctypes.data if color is not None else None, zp, 1 if clear else 0)
             if rc != 0:
-                raise RuntimeError("RefCuda_RenderViews failed")
+                raise RuntimeError("RefCuda_RenderViews failed: " + self.host.lib.xh_last_error().decode(errors="replace"))
             self.last_seconds = None
         else:
             x, y, w, h = viewport or (0, 0, self.width, self.height)
