@@ -44,19 +44,52 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
-    ap.add_argument("--views", type=int, default=256, help="views per GPU per step")
-    ap.add_argument("--width", type=int, default=320)
-    ap.add_argument("--height", type=int, default=240)
-    ap.add_argument("--map", default="small", choices=["tiny", "small", "medium", "large"])
+    ap.add_argument("--config", default=None, choices=["c2", "c3", "c5"],
+                    help="BASELINE.json config: c2 = 256 views/GPU 320x240 Map S (default at 1 GPU), c3 = 1920x1080 views of Map L with "
+                         "light styles changing every step (surface cache rebuilt per step), c5 = 4096 views/GPU 320x240 Map S with water (default at > 1 GPU)")
+    ap.add_argument("--views", type=int, default=None, help="views per GPU per step")
+    ap.add_argument("--width", type=int, default=None)
+    ap.add_argument("--height", type=int, default=None)
+    ap.add_argument("--map", default=None, choices=["tiny", "small", "medium", "large"])
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    return ap.parse_args()
+    a = ap.parse_args()
+    if a.config is None:
+        a.config = "c2" if a.gpus <= 1 else "c5"
+    preset = {"c2": (256, 320, 240, "small"), "c3": (8, 1920, 1080, "large"), "c5": (4096, 320, 240, "small")}[a.config]
+    a.views = a.views or preset[0]
+    a.width = a.width or preset[1]
+    a.height = a.height or preset[2]
+    a.map = a.map or preset[3]
+    a.map_kw = {"water_prob": (1, 5)} if a.config == "c5" else {}
+    a.rebuild = a.config == "c3"
+    a.cvars = {"sw_maxsurfs": 40000, "sw_maxedges": 160000} if a.config == "c3" else {}
+    return a
+
+
+C3_PATTERNS = {1: "mmnmmommommnonmmonqnmmo", 2: "abcdefghijklmnopqrstuvwxyzyxwvutsrqponmlkjihgfedcba", 3: "mamamamamama",
+               4: "mmamammmmammamamaaamammma", 5: "jklmnopqrstuvwxyzyxwvutsrqponmlkj", 6: "nmonqnmomnmomomno",
+               7: "mmmaaaabcdefgmmmmaaaammmaamm", 8: "mmmaaammmaaammmabcdefaaaammmmabcdefmmmaaaa", 9: "aaaaaaaazzzzzzzz",
+               10: "mmamammmmammamamaaamammma", 11: "abcdefghijklmnopqrrqponmlkjihgfedcba"}
+
+
+def advance_styles(r, step):
+    """config c3: every step is a new timestamp - the animated light styles take new values, so every surface-cache
+    block that lists one of them is rebuilt (D_CacheSurface's staleness test, ref/soft/r_surf.c:1090)"""
+    for k, p in C3_PATTERNS.items():
+        r.set_lightstyle(k, p, time=step / 60.0 * 7 + 0.05)
+    r.set_time(1.0 + step / 60.0)
+    r.run_lightstyles()
 
 
 def workload(args, world):
+    what = {"c2": "static lightmaps (BASELINE.json configs[1])",
+            "c3": "light styles 1..11 change every step: every surface-cache block that lists one is rebuilt per step (BASELINE.json configs[2])",
+            "c5": "turbulent water on ~10 % of the floor (BASELINE.json configs[4], per GPU)"}[args.config]
+    mapname = {"small": "S (~1.7k faces; with pools ~2.2k)", "large": "L (~33k faces)", "medium": "M (~12.5k faces)", "tiny": "tiny"}[args.map]
     return {
-        "workload": f"{args.views} batched camera views/GPU at {args.width}x{args.height}, synthetic BSP30 Map "
-                    f"{'S (~1.7k faces)' if args.map == 'small' else args.map}, static lightmaps (BASELINE.json configs[1])",
+        "workload": f"{args.config}: {args.views} batched camera views/GPU at {args.width}x{args.height}, synthetic BSP30 Map {mapname}, {what}",
+        "config_id": args.config,
         "views_per_gpu": args.views, "width": args.width, "height": args.height, "map": args.map,
         "sharding": f"views x{world}, scene replicated, no data-path collective",
         "l2": "flushed with a 256 MB write between timed steps",
@@ -134,8 +167,8 @@ def _soft_worker(conn, args_d, lo, hi, ncams):
             pass
         pkg = importlib.import_module("xash3d-fwgs_b200")
         scene = importlib.import_module("xash3d-fwgs_b200.scene")
-        m = scene.make_map(args_d["map"], ncameras=ncams)
-        r = scene.Renderer(pkg.REF_SOFT_PATH, args_d["width"], args_d["height"], m)
+        m = scene.make_map(args_d["map"], ncameras=ncams, **args_d["map_kw"])
+        r = scene.Renderer(pkg.REF_SOFT_PATH, args_d["width"], args_d["height"], m, cvars=args_d["cvars"])
         cams = m.cameras[lo:hi]
         out = (np.empty((len(cams), args_d["height"], args_d["width"]), np.uint16), np.empty((len(cams), args_d["height"], args_d["width"]), np.int16))
         conn.send("ready")
@@ -143,6 +176,8 @@ def _soft_worker(conn, args_d, lo, hi, ncams):
             cmd = conn.recv()
             if cmd == "quit":
                 break
+            if args_d["rebuild"]:
+                advance_styles(r, cmd[1])
             t0 = time.perf_counter()
             r.render_views(cams, out=out)
             conn.send((time.perf_counter() - t0, r.last_seconds))
@@ -161,7 +196,8 @@ class SoftPool:
         self.procs = []
         for i in range(self.n):
             a, b = ctx.Pipe()
-            d = {"map": args.map, "width": args.width, "height": args.height, "cpu": cpus[i % len(cpus)]}
+            d = {"map": args.map, "width": args.width, "height": args.height, "cpu": cpus[i % len(cpus)], "map_kw": args.map_kw,
+                 "cvars": args.cvars, "rebuild": args.rebuild}
             p = ctx.Process(target=_soft_worker, args=(b, d, int(bounds[i]), int(bounds[i + 1]), args.views), daemon=True)
             p.start()
             self.procs.append((p, a))
@@ -170,11 +206,11 @@ class SoftPool:
             if msg != "ready":
                 raise RuntimeError(f"ref_soft worker failed: {msg}")
 
-    def step(self):
+    def step(self, k=0):
         """all workers render their slice of the batch once; -> (wall seconds, max seconds inside R_RenderFrame)"""
         t0 = time.perf_counter()
         for _, a in self.procs:
-            a.send("go")
+            a.send(("go", k))
         res = [a.recv() for _, a in self.procs]
         wall = time.perf_counter() - t0
         if any(r[0] == "error" for r in res):
@@ -197,11 +233,11 @@ def run_reference(args):
         return
     ncores = len(os.sched_getaffinity(0))
     pool = SoftPool(args, ncores)
-    for _ in range(args.warmup):
-        pool.step()
+    for k in range(args.warmup):
+        pool.step(k)
     walls, inner = [], []
-    for _ in range(args.steps):
-        w, i = pool.step()
+    for k in range(args.steps):
+        w, i = pool.step(args.warmup + k)
         walls.append(w)
         inner.append(i)
     pool.close()
@@ -226,19 +262,22 @@ def cpu_baseline_one_core(args):
     """the oracle on ONE host core, a bounded sample of the same workload (reported baseline, not the target)"""
     pkg = importlib.import_module("xash3d-fwgs_b200")
     scene = importlib.import_module("xash3d-fwgs_b200.scene")
-    m = scene.make_map(args.map, ncameras=args.views)
-    r = scene.Renderer(pkg.REF_SOFT_PATH, args.width, args.height, m)
-    cams = m.cameras[: args.views]
+    m = scene.make_map(args.map, ncameras=args.views, **args.map_kw)
+    r = scene.Renderer(pkg.REF_SOFT_PATH, args.width, args.height, m, cvars=args.cvars)
+    cams = m.cameras[: min(args.views, 256)]
     out = (np.empty((len(cams), args.height, args.width), np.uint16), np.empty((len(cams), args.height, args.width), np.int16))
     r.render_views(cams, out=out)  # warm: fills the surface cache
     secs, passes, t0 = 0.0, 0, time.perf_counter()
     while time.perf_counter() - t0 < args.cpu_seconds and passes < 1000:
+        if args.rebuild:
+            advance_styles(r, passes + 1)
         r.render_views(cams, out=out)
         secs += r.last_seconds
         passes += 1
     px = passes * len(cams) * args.width * args.height
     return {"value": px / secs / 1e6, "unit": UNIT, "cores": 1, "kind": "reference",
-            "sample": f"{passes} passes of the {len(cams)}-view batch ({secs:.1f} s inside GL_RenderFrame), warm surface cache, gcc -O2"}
+            "sample": f"{passes} passes of {len(cams)} views of the batch ({secs:.1f} s inside GL_RenderFrame), "
+                      + ("light styles advanced before every pass" if args.rebuild else "warm surface cache") + ", gcc -O2"}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -271,15 +310,18 @@ def run_cuda(args):
     pkg = importlib.import_module("xash3d-fwgs_b200")
     scene = importlib.import_module("xash3d-fwgs_b200.scene")
     shard = importlib.import_module("xash3d-fwgs_b200.shard")
-    m = scene.make_map(args.map, ncameras=args.views * world)
+    m = scene.make_map(args.map, ncameras=args.views * world, **args.map_kw)
     lo, hi = shard.view_range(args.views * world, rank, world)  # this rank's slice of the global camera list
     cams = m.cameras[lo:hi]
     r = scene.Renderer(pkg.REF_CUDA_PATH, args.width, args.height, m, cvars={"cu_device": local})
+    if args.rebuild:
+        advance_styles(r, 0)
     n, w, h = len(cams), args.width, args.height
     px = n * w * h
 
     # pinned host landing zone for the e2e leg (torch only provides the pinned allocation)
     pin = torch.empty((n, h, w), dtype=torch.int16).pin_memory()
+    pin_z = torch.empty((n, h, w), dtype=torch.int16).pin_memory()
     vp = r.viewpasses(cams)
     r.render_prepared(vp, pin.data_ptr(), None)  # uploads the batch, builds the surface cache blocks it needs
     ctr0 = r.counters()
@@ -288,11 +330,11 @@ def run_cuda(args):
         raise SystemExit(f"bench.py: capacity overflow {overflow} - numbers would be invalid")
 
     # -- value: device stages, inputs resident, CUDA events inside the plugin, L2 flushed between steps
-    r.bench_resident(max(args.warmup, 3), flush_l2=True)
+    r.bench_resident(max(args.warmup, 3), flush_l2=True, rebuild_cache=args.rebuild)
     sampler = ClockSampler(local) if rank == 0 else None
     barrier()
     l0 = r.launch_count()
-    ms, stages = r.bench_resident(args.steps, flush_l2=True)
+    ms, stages = r.bench_resident(args.steps, flush_l2=True, rebuild_cache=args.rebuild)
     launches = r.launch_count() - l0
     barrier()
     ms_step = allmax(ms)
@@ -316,15 +358,25 @@ def run_cuda(args):
     ms_blit = allmax(float(np.median(blit_ms[max(args.warmup, 3):])))
 
     # -- e2e: the public C-ABI call with host buffers (H2D view descriptors, D2H colour frames), wall clock
-    for _ in range(max(args.warmup, 3)):
-        r.render_prepared(vp, pin.data_ptr(), None)
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        r.render_prepared(vp, pin.data_ptr(), None)
-    torch.cuda.synchronize()
-    e2e_s = allmax((time.perf_counter() - t0) / args.steps)
-    barrier()
+    def e2e_leg(zptr):
+        for k in range(max(args.warmup, 3)):
+            if args.rebuild:
+                advance_styles(r, k + 1)
+            r.render_prepared(vp, pin.data_ptr(), zptr)
+        barrier()
+        t0 = time.perf_counter()
+        for k in range(args.steps):
+            if args.rebuild:
+                advance_styles(r, k + 100)
+            r.render_prepared(vp, pin.data_ptr(), zptr)
+        torch.cuda.synchronize()
+        secs = allmax((time.perf_counter() - t0) / args.steps)
+        barrier()
+        return secs
+
+    e2e_s = e2e_leg(None)
+    h2d = r.batch_h2d_bytes()
+    e2e_z_s = e2e_leg(pin_z.data_ptr())
     clocks = sampler.stop() if sampler else None
 
     # counters of the last batch, summed over ranks (the only collective: < 1 KiB, off the data path)
@@ -345,8 +397,12 @@ def run_cuda(args):
             "frames_per_s": n * world / (ms_step * 1e-3),
             "stage_ms": {"vis_walk": stages[0], "faces_edges": stages[1], "surface_cache": stages[2], "spans": stages[3], "draw": stages[4],
                          "note": "the surface-cache kernels run on a side stream beside span generation: their time overlaps spans and is not part of the sum"},
-            "e2e": {"value": total_px / e2e_s / 1e6, "unit": UNIT, "h2d_bytes_per_step": n * 56, "d2h_bytes_per_step": px * 2,
-                    "ms_per_step": e2e_s * 1e3, "note": "RefCuda_RenderViews: ref_viewpass_t array in, colour frames out to pinned host memory"},
+            "e2e": {"value": total_px / e2e_s / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": px * 2 + 512,
+                    "ms_per_step": e2e_s * 1e3,
+                    "note": "RefCuda_RenderViews, host buffers: per-view constants (+ light styles when they change) host->device, colour frames "
+                            "(what an observation consumer takes) device->host into pinned memory, 512 B of counters"},
+            "e2e_colour_and_z": {"value": total_px / e2e_z_s / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": px * 4 + 512,
+                                 "ms_per_step": e2e_z_s * 1e3, "note": "the same call with the z buffers copied out as well (what the reference arm leaves in host memory)"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": "k_draw", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": measured_traffic(), "algorithmic_bytes_per_launch": BYTES_PER_PIXEL * px, "peak_source": peak_src,
@@ -355,6 +411,7 @@ def run_cuda(args):
                                        "peak": peak, "unit": "GB/s", "frac": 4 * cache_texels / (ms_cache * 1e-3) / 1e9 / peak,
                                        "algorithmic_bytes_per_launch": 4 * cache_texels, "kernel_ms": ms_cache, "traffic": measured_traffic("k_cache_build_dram_bytes_per_launch"),
                                        "note": "forced rebuild of every (face, mip) block this rank's batch samples: 4 B per cache texel (2 B texel read + 2 B written), luxel bytes not counted"},
+            "value_note": ("value is timed with EVERY surface-cache block the batch samples invalidated before each step (a superset of the blocks whose light styles changed)" if args.rebuild else None),
             "roofline_display_tail": {"bound": "hbm", "kernel": "k_blit<4> (pixel_t -> XRGB8888)", "achieved": 6 * px / (ms_blit * 1e-3) / 1e9, "peak": peak,
                                       "unit": "GB/s", "frac": 6 * px / (ms_blit * 1e-3) / 1e9 / peak, "algorithmic_bytes_per_launch": 6 * px,
                                       "kernel_ms": ms_blit, "traffic": None, "note": "2 B pixel_t read + 4 B display pixel written; 256 KB screen map in L2; not part of value / e2e"},

@@ -63,6 +63,9 @@ REF_CUDA_EXPORT int RefCuda_ReadSurfaceCache( int surf, int mip, unsigned short 
 /* Counters of the last batch (rc_shared.h RC_CTR_*), kernels launched since R_Init, device name. */
 REF_CUDA_EXPORT int RefCuda_GetCounters( unsigned long long *out, int n );
 REF_CUDA_EXPORT unsigned long long RefCuda_LaunchCount( void );
+/* host->device bytes the last RefCuda_RenderViews call uploaded: per-view constants, light style values, dynamic
+ * lights, entity state (what a harness reports as the batch's input traffic) */
+REF_CUDA_EXPORT unsigned long long RefCuda_BatchH2DBytes( void );
 REF_CUDA_EXPORT const char *RefCuda_DeviceName( void );
 
 #ifdef __cplusplus

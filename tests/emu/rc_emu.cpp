@@ -83,6 +83,7 @@ void rc_dev_shutdown( void ) {}
 const char *rc_dev_last_error( void ) { return E.err; }
 const char *rc_dev_name( void ) { return "cpu-emulation (debug harness)"; }
 uint64_t rc_dev_launch_count( void ) { return 0; }
+uint64_t rc_dev_h2d_bytes( int ) { return 0; }
 
 int rc_dev_upload_luts( const uint16_t *colormap, const uint16_t *lightgamma, const int32_t *sintable )
 {

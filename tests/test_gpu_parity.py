@@ -2,8 +2,9 @@
 oracle (unmodified ref_soft on the host CPU) on the same seeded inputs, against the committed goldens, and at
 BASELINE.json's full size through size-independent properties.
 
-Bars (BASELINE.json north_star): surface-cache blocks bit-exact; framebuffer and z-buffer >= 99.9 % identical
-pixels with every residual pixel within 1 px of a surface boundary of the reference image.
+Bars: BASELINE.json's north_star allows 99.9 % identical framebuffer pixels; what was measured on every configuration is
+100 %, so the tests demand equality (np.array_equal) of colour, z and surface-cache blocks.  A test that keeps a looser
+bar says why.
 """
 import hashlib
 import importlib
@@ -13,7 +14,6 @@ import pytest
 
 pytestmark = pytest.mark.gpu
 
-TOL = 0.999
 
 
 def sha(a):
@@ -68,8 +68,8 @@ def test_tiny_map_matches_committed_golden_frames(pkg, scene, golden_frames):
     assert hashlib.sha256(m.bsp).hexdigest() == c["bsp_sha256"]
     cu = scene.Renderer(pkg.REF_CUDA_PATH, 320, 240, m)
     col, z = cu.render_views(m.cameras[:8])
-    assert (col == data["tiny_colour"]).mean() >= TOL
-    assert (z == data["tiny_z"]).mean() >= TOL
+    assert np.array_equal(col, data["tiny_colour"])
+    assert np.array_equal(z, data["tiny_z"])
     # cache blocks the oracle held at the end of its run: bit-exact
     hit = 0
     for key, h in c["cache_blocks_sha256"].items():
@@ -88,10 +88,9 @@ def test_small_map_matches_committed_golden_hashes(pkg, scene, golden_frames, ca
     m = scene.make_map("small", ncameras=16)
     cu = scene.Renderer(pkg.REF_CUDA_PATH, c["width"], c["height"], m)
     col, z = cu.render_views(m.cameras[: c["views"]])
-    same = sum(sha(col[i]) == c["colour_sha256"][i] for i in range(c["views"]))
-    samez = sum(sha(z[i]) == c["z_sha256"][i] for i in range(c["views"]))
-    # whole-frame hashes: a frame with even one edge pixel off fails its hash, so allow a minority
-    assert same >= c["views"] * 3 // 4 and samez >= c["views"] * 3 // 4, (same, samez)
+    for i in range(c["views"]):
+        assert sha(col[i]) == c["colour_sha256"][i], i
+        assert sha(z[i]) == c["z_sha256"][i], i
     for key, h in c["cache_blocks_sha256"].items():
         s, mip = map(int, key.split("."))
         b = cu.cache_block(s, mip)
@@ -100,17 +99,14 @@ def test_small_map_matches_committed_golden_hashes(pkg, scene, golden_frames, ca
 
 
 def test_frames_match_oracle_c2_sample(cu_small, so_small):
-    """64 of the C2 cameras, 320x240: the tolerance of the report is stated here."""
+    """64 of the C2 cameras, 320x240."""
     cu, m = cu_small
     so, _ = so_small
     cams = m.cameras[:64]
     cc, cz = cu.render_views(cams)
     rc, rz = so.render_views(cams)
-    assert (cc == rc).mean() >= TOL, (cc == rc).mean()
-    assert (cz == rz).mean() >= TOL, (cz == rz).mean()
-    for i in range(len(cams)):
-        assert (cc[i] == rc[i]).mean() >= 0.995, i
-    assert residuals_on_boundaries(rc, rz, cc) == 0
+    assert np.array_equal(cc, rc), f"colour identical {(cc == rc).mean():.6f}, off-boundary residuals {residuals_on_boundaries(rc, rz, cc)}"
+    assert np.array_equal(cz, rz), (cz == rz).mean()
     ctr = cu.counters()
     assert all(v == 0 for k, v in ctr.items() if k.startswith("overflow")), ctr
     assert ctr["views"] == 64 and ctr["pixels"] == 64 * 320 * 240
@@ -152,7 +148,7 @@ def test_animated_lightstyles_rebuild_cache_bit_exact(pkg, scene):
             r.run_lightstyles()
         cc, cz = cu.render_views(m.cameras[:4])
         rc, rz = so.render_views(m.cameras[:4])
-        assert (cc == rc).mean() >= TOL and (cz == rz).mean() >= TOL, step
+        assert np.array_equal(cc, rc) and np.array_equal(cz, rz), step
         n = 0
         for s in range(so.host.world_info()["numsurfaces"]):
             for mip in range(4):
@@ -177,16 +173,29 @@ def test_water_and_sky_surfaces(pkg, scene):
         cams[:, 3] = 25.0  # look down at the pools
         cc, cz = cu.render_views(cams)
         rc, rz = so.render_views(cams)
-        assert (cc == rc).mean() >= TOL and (cz == rz).mean() >= TOL, t
+        assert np.array_equal(cc, rc) and np.array_equal(cz, rz), t
 
 
-def test_no_clear_keeps_previous_pixels(cu_small, so_small):
-    """F8: ref_soft never clears; uncovered pixels keep the previous frame's content."""
-    cu, m = cu_small
-    so, _ = so_small
-    a, _ = cu.render_views(m.cameras[:2], clear=True)
-    b, _ = cu.render_views(m.cameras[:2], clear=False)
-    assert np.array_equal(a, b)
+def test_no_clear_keeps_previous_pixels(pkg, scene):
+    """F8: ref_soft never clears; pixels no surface covers keep the previous frame's content.  Frame A is an ordinary
+    view, frame B (clear=0) looks at the world from outside its hull with r_novis 1: only the faces that look at the
+    eye are drawn, the rest of B's buffer must still hold A - in both renderers."""
+    m = scene.make_map("tiny", ncameras=16)
+    cv = {"r_novis": 1}
+    cu = scene.Renderer(pkg.REF_CUDA_PATH, 320, 240, m, cvars=cv)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m, cvars=cv)
+    g = m.grid.shape
+    outside = np.array([[m.origin[0] - 200.0, m.origin[1] + g[1] * 16.0, m.origin[2] + g[2] * 16.0, 5.0, 0.0, 0.0],
+                        [m.origin[0] + g[0] * 16.0, m.origin[1] - 300.0, m.origin[2] + 300.0, 40.0, 90.0, 0.0]], np.float32)
+    for i in range(2):
+        a, az = cu.render_views(m.cameras[i : i + 1], clear=True)
+        b, bz = cu.render_views(outside[i : i + 1], clear=False)
+        ra, raz = so.render_views(m.cameras[i : i + 1], clear=True)
+        rb, rbz = so.render_views(outside[i : i + 1], clear=False)
+        assert np.array_equal(a, ra) and np.array_equal(az, raz)
+        assert np.array_equal(b, rb) and np.array_equal(bz, rbz)
+        kept = (rb == ra) & (rbz == raz)
+        assert 0.02 < kept.mean() < 0.98, kept.mean()  # B covers part of the screen only
 
 
 def test_partial_viewport(pkg, scene):
@@ -200,13 +209,13 @@ def test_partial_viewport(pkg, scene):
     vp = (40, 30, 200, 150)
     cc, cz = cu.render_views(m.cameras[:4], viewport=vp)
     rc, rz = so.render_views(m.cameras[:4], viewport=vp)
-    assert (cc == rc).mean() >= TOL and (cz == rz).mean() >= TOL
+    assert np.array_equal(cc, rc) and np.array_equal(cz, rz)
     assert not cc[:, :30].any() and not cc[:, :, :40].any() and not cc[:, 180:].any() and not cc[:, :, 240:].any()
 
 
-def test_full_c2_batch_properties(cu_small, so_small):
-    """BASELINE.json configs[1] at full size (256 views, 320x240): determinism, batch-split invariance,
-    no capacity overflow, and a spot check of 8 views against the oracle."""
+def test_full_c2_batch_matches_oracle(cu_small, so_small):
+    """BASELINE.json configs[1] at full size (256 views, 320x240): every view equals the oracle's; determinism,
+    batch-split invariance, no capacity overflow."""
     cu, m = cu_small
     so, _ = so_small
     cams = m.cameras[:256]
@@ -218,31 +227,31 @@ def test_full_c2_batch_properties(cu_small, so_small):
     h1, _ = cu.render_views(cams[:100])
     h2, _ = cu.render_views(cams[100:])
     assert np.array_equal(a[:100], h1) and np.array_equal(a[100:], h2)  # views are independent
-    idx = [3, 77, 128, 200, 255, 19, 91, 160]
-    rc, rz = so.render_views(cams[idx])
-    assert (a[idx] == rc).mean() >= TOL and (az[idx] == rz).mean() >= TOL
+    rc, rz = so.render_views(cams)
+    assert np.array_equal(a, rc) and np.array_equal(az, rz)
     assert (a != 0).mean() > 0.95  # the camera list looks at geometry, not at void
 
 
-def test_c3_mechanism_medium_map_1080p(pkg, scene):
-    """C3 at a size the generator finishes quickly: 1920x1080 views of Map M (~12.5k faces, extra light styles),
-    animated style values forcing cache rebuilds.  SURVEY F9: ref_soft silently drops faces past sw_maxsurfs
-    (2000) and edges past sw_maxedges (4000) - both raised in the oracle, before R_NewMap."""
-    m = scene.make_map("medium", ncameras=8)
-    cu = scene.Renderer(pkg.REF_CUDA_PATH, 1920, 1080, m)
-    so = scene.Renderer(pkg.REF_SOFT_PATH, 1920, 1080, m, cvars={"sw_maxsurfs": 60000, "sw_maxedges": 250000})
-    pats = {1: "mmnmmommommnonmmonqnmmo", 2: "abcdefghijklmnopqrstuvwxyzyxwvutsrqponmlkjihgfedcba", 3: "mamamamamama"}
-    for step in range(2):
+C3_PATTERNS = {1: "mmnmmommommnonmmonqnmmo", 2: "abcdefghijklmnopqrstuvwxyzyxwvutsrqponmlkjihgfedcba", 3: "mamamamamama",
+               4: "mmamammmmammamamaaamammma", 5: "jklmnopqrstuvwxyzyxwvutsrqponmlkj", 6: "nmonqnmomnmomomno",
+               7: "mmmaaaabcdefgmmmmaaaammmaamm", 8: "mmmaaammmaaammmabcdefaaaammmmabcdefmmmaaaa", 9: "aaaaaaaazzzzzzzz",
+               10: "mmamammmmammamamaaamammma", 11: "abcdefghijklmnopqrrqponmlkjihgfedcba"}
+
+
+def run_c3(cu, so, cams, steps):
+    for step in range(steps):
         for r in (cu, so):
-            for k, p in pats.items():
-                r.set_lightstyle(k, p, time=step * 0.1 + 0.05)
-            r.set_time(1.0 + step * 0.1)
+            for k, p in C3_PATTERNS.items():
+                r.set_lightstyle(k, p, time=step / 60.0 * 7 + 0.05)
+            r.set_time(1.0 + step / 60.0)
             r.run_lightstyles()
-        cc, cz = cu.render_views(m.cameras[:4])
-        rc, rz = so.render_views(m.cameras[:4])
-        assert (cc == rc).mean() >= TOL and (cz == rz).mean() >= TOL, (step, (cc == rc).mean())
+        cc, cz = cu.render_views(cams)
+        rc, rz = so.render_views(cams)
+        assert np.array_equal(cc, rc) and np.array_equal(cz, rz), (step, (cc == rc).mean())
         ctr = cu.counters()
         assert all(v == 0 for k, v in ctr.items() if k.startswith("overflow")), ctr
+        if step:
+            assert ctr["cache_blocks"] > 0  # style values changed: blocks were rebuilt
         n = 0
         for s in range(0, so.host.world_info()["numsurfaces"], 7):
             for mip in range(4):
@@ -251,6 +260,76 @@ def test_c3_mechanism_medium_map_1080p(pkg, scene):
                     assert np.array_equal(a, b), (step, s, mip)
                     n += 1
         assert n > 0
+
+
+def test_c3_mechanism_medium_map_1080p(pkg, scene):
+    """1920x1080 views of Map M (~12.5k faces, light styles 1..11 on a quarter of the faces), style values changing
+    every frame.  SURVEY F9: ref_soft silently drops faces past sw_maxsurfs (2000) and edges past sw_maxedges (4000) -
+    both raised in the oracle, before R_NewMap."""
+    m = scene.make_map("medium", ncameras=8)
+    cu = scene.Renderer(pkg.REF_CUDA_PATH, 1920, 1080, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 1920, 1080, m, cvars={"sw_maxsurfs": 60000, "sw_maxedges": 250000})
+    run_c3(cu, so, m.cameras[:4], 2)
+
+
+def test_c3_map_l_1080p_at_stated_size(pkg, scene):
+    """BASELINE.json configs[2]: 1920x1080 views of Map L (~33k faces), animated light styles 1..11 forcing surface
+    cache rebuilds every frame; the oracle runs with sw_maxsurfs 40000 / sw_maxedges 160000."""
+    m = scene.make_map("large", ncameras=8)
+    assert m.stats["faces"] >= 30000
+    cu = scene.Renderer(pkg.REF_CUDA_PATH, 1920, 1080, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 1920, 1080, m, cvars={"sw_maxsurfs": 40000, "sw_maxedges": 160000})
+    run_c3(cu, so, m.cameras[:8], 3)
+
+
+def test_c5_4096_views_with_water_match_oracle(pkg, scene):
+    """BASELINE.json configs[4] per GPU: 4096 views at 320x240 on Map S with water on ~10 % of the floor (Turbulent8),
+    every one of the 314 Mpixel compared with the oracle."""
+    m = scene.make_map("small", ncameras=4096, water_prob=(1, 5))
+    cu = scene.Renderer(pkg.REF_CUDA_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    for r in (cu, so):
+        r.set_time(2.37)
+    cams = m.cameras[:4096]
+    a, az = cu.render_views(cams)
+    ctr = cu.counters()
+    assert ctr["views"] == 4096 and all(v == 0 for k, v in ctr.items() if k.startswith("overflow")), ctr
+    for lo in range(0, 4096, 512):
+        rc, rz = so.render_views(cams[lo : lo + 512])
+        assert np.array_equal(a[lo : lo + 512], rc) and np.array_equal(az[lo : lo + 512], rz), lo
+
+
+@pytest.mark.parametrize("case", ["fov60", "fov110", "roll", "mipcap2", "mipscale05", "novis", "fullbright", "in_solid"])
+def test_view_and_cvar_variants_match_oracle(pkg, scene, case):
+    """Inputs the C2 camera list never has: other fields of view, camera roll, sw_mipcap / sw_mipscale, r_novis,
+    r_fullbright, an eye inside solid."""
+    m = scene.make_map("small", ncameras=32)
+    cv = {"mipcap2": {"sw_mipcap": 2}, "mipscale05": {"sw_mipscale": 0.5}, "novis": {"r_novis": 1}, "fullbright": {"r_fullbright": 1}}.get(case, {})
+    cu = scene.Renderer(pkg.REF_CUDA_PATH, 320, 240, m, cvars=cv)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m, cvars=cv)
+    cams = np.array(m.cameras[:16], dtype=np.float32)
+    fov = {"fov60": 60.0, "fov110": 110.0}.get(case, 90.0)
+    if case == "roll":
+        cams[:, 5] = np.linspace(-75.0, 80.0, len(cams))
+    if case == "in_solid":
+        cams[:, 2] = m.origin[2] + 12.0  # inside the bottom slab
+        cams[:, 3] = -35.0
+    if case == "fullbright":
+        for r in (cu, so):
+            r.run_lightstyles()
+    cc, cz = cu.render_views(cams, fov_x=fov)
+    rc, rz = so.render_views(cams, fov_x=fov)
+    assert np.array_equal(cc, rc) and np.array_equal(cz, rz), (case, (cc == rc).mean())
+
+
+def test_map_without_vis_data(pkg, scene):
+    """A BSP whose leaves carry no PVS rows (visofs -1, empty visibility lump): everything is potentially visible."""
+    m = scene.make_map("tiny", ncameras=16, novis=True)
+    cu = scene.Renderer(pkg.REF_CUDA_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    cc, cz = cu.render_views(m.cameras[:8])
+    rc, rz = so.render_views(m.cameras[:8])
+    assert np.array_equal(cc, rc) and np.array_equal(cz, rz)
 
 
 DISPLAY_FORMATS = [(2, 0xF800, 0x07E0, 0x001F), (4, 0x00FF0000, 0x0000FF00, 0x000000FF)]

@@ -64,6 +64,8 @@ int rc_dev_read_cache_block( int surf, int mip, uint16_t *out, int maxtexels, in
 int rc_dev_read_counters( uint64_t *out, int n );
 int rc_dev_read_view_surfs( int view, rc_surf_t *out, int max, int *n );
 int rc_dev_read_view_edges( int view, rc_edge_t *out, int max, int *n );
+/* host->device bytes uploaded since the last call with reset != 0 */
+uint64_t rc_dev_h2d_bytes( int reset );
 /* launch counter: kernels of ours launched since init */
 uint64_t rc_dev_launch_count( void );
 

@@ -267,7 +267,7 @@ __global__ void __launch_bounds__( CACHE_THREADS ) k_cache_build( rc_scene_t sc,
 		const int32_t size = smax * tmax;
 		if( size > CACHE_LUXCAP )
 		{
-			if( tid == 0 ) atomicAdd( &w.counters[RC_CTR_OVERFLOW_CANDS], 1ull );
+			if( tid == 0 ) atomicAdd( &w.counters[RC_CTR_OVERFLOW_CACHE], 1ull );
 			continue;
 		}
 		const uint32_t dbits = w.ndlights ? w.dlightbits[slot >> 2] : 0u;
@@ -456,7 +456,7 @@ __global__ void __launch_bounds__( 256 ) k_blit( const uint16_t *__restrict__ co
 struct Dev
 {
 	bool ready = false;
-	int device = 0;
+	int device = 0, num_sms = 148;
 	char name[256] = "";
 	char err[512] = "";
 	cudaStream_t stream = nullptr, copy = nullptr;
@@ -466,7 +466,7 @@ struct Dev
 	cudaEvent_t ev_cache[RC_MAX_SLICES][2] = {};           /* start / end of those */
 	bool cache_aside = true;                               /* false: on the slice's own stream (the bench times the kernels alone) */
 	cudaEvent_t ev[8] = {};
-	uint64_t launches = 0;
+	uint64_t launches = 0, h2d_bytes = 0;
 
 	rc_scene_t sc{};            /* device pointers */
 	std::vector<rc_surface_t> h_surfaces;
@@ -490,6 +490,12 @@ struct Dev
 	/* batch work buffers (grown on demand) */
 	rc_work_t w{};
 	int cap_views = 0, cap_w = 0, cap_h = 0;
+	/* per-view capacities: they start from what a view typically needs and follow the counters of the batches
+	 * rendered so far (a batch that overflows one is re-run with a larger one), never the worst case of the map */
+	int cap_cands = 0, cap_edges = 0, cap_blk_events = 0;
+	bool caps_dirty = false;
+	int vw_grid = 0;                         /* k_viswalk: resident blocks, persistent over views */
+	unsigned long long *h_counters = nullptr; /* pinned mirror of the batch counters, copied at the end of every batch */
 	rc_view_t *d_views = nullptr;
 	void *d_work[20] = {};
 	bool have_batch = false;
@@ -542,16 +548,26 @@ void free_batch()
 
 int ensure_batch( int nviews, int width, int height )
 {
-	if( nviews <= D.cap_views && width == D.cap_w && height == D.cap_h )
+	if( nviews <= D.cap_views && width == D.cap_w && height == D.cap_h && !D.caps_dirty )
 		return 0;
+	const int keep = nviews > D.cap_views ? nviews : D.cap_views;
+	const bool same_size = width == D.cap_w && height == D.cap_h;
 	free_batch();
 	const rc_scene_t &sc = D.sc;
 	rc_work_t &w = D.w;
-	int cap = nviews;
+	int cap = same_size ? keep : nviews;
 	w.width = width; w.height = height;
-	w.max_cands = sc.numsurfaces < 65000 ? ( sc.numsurfaces > 0 ? sc.numsurfaces : 1 ) : 65000;
+	const int worst_cands = sc.numsurfaces < 65000 ? ( sc.numsurfaces > 0 ? sc.numsurfaces : 1 ) : 65000;
 	long long me = (long long)sc.numsurfedges + sc.numsurfaces + 64;
-	w.max_edges = (int32_t)( me < 262144 ? me : 262144 );
+	const int worst_edges = (int32_t)( me < 2000000 ? me : 2000000 );
+	if( !D.cap_cands ) D.cap_cands = worst_cands < 2048 ? worst_cands : 2048;
+	if( D.cap_cands > worst_cands ) D.cap_cands = worst_cands;
+	if( !D.cap_edges ) D.cap_edges = 6 * D.cap_cands + 64;
+	if( D.cap_edges > worst_edges ) D.cap_edges = worst_edges;
+	if( !D.cap_blk_events || !same_size ) D.cap_blk_events = SP_LINES * ( width <= 640 ? 192 : 384 );
+	D.caps_dirty = false;
+	w.max_cands = D.cap_cands;
+	w.max_edges = D.cap_edges;
 	w.visbytes_padded = ( sc.visbytes + 15 ) & ~15;
 	w.nodewords = ( sc.numnodes + 31 ) / 32 + 1;
 	w.leafwords = ( sc.numleafs + 31 ) / 32 + 1;
@@ -576,10 +592,17 @@ int ensure_batch( int nviews, int width, int height )
 		}
 		w.vis_smem = (int32_t)need;
 	}
+	{
+		/* k_viswalk blocks are persistent over views: as many as the device keeps resident */
+		int per_sm = 0;
+		CK( cudaOccupancyMaxActiveBlocksPerMultiprocessor( &per_sm, k_viswalk<VW_NTHREADS>, VW_NTHREADS, (size_t)w.vis_smem ));
+		if( per_sm < 1 ) per_sm = 1;
+		D.vw_grid = per_sm * D.num_sms;
+	}
 
 	int k = 0;
 #define WALLOC( field, type, count ) do { type *p = nullptr; if( dalloc( &p, (size_t)( count )) != 0 ) return -1; w.field = p; D.d_work[k++] = p; } while( 0 )
-	WALLOC( walkstack, int32_t, (size_t)cap * w.stack_ints );
+	WALLOC( walkstack, int32_t, (size_t)D.vw_grid * RC_MAX_SLICES * w.stack_ints );
 	WALLOC( cands, rc_cand_t, (size_t)cap * w.max_cands );
 	WALLOC( surfs, rc_surf_t, (size_t)cap * w.max_cands );
 	WALLOC( edges, rc_edge_t, (size_t)cap * w.max_edges );
@@ -587,7 +610,7 @@ int ensure_batch( int nviews, int width, int height )
 	WALLOC( nedges, int32_t, cap );
 	w.nbands = ( height + SP_LINES - 1 ) / SP_LINES;
 	w.ev_ecap = width * height <= 640 * 480 ? EV_ECAP_SMALL : EV_ECAP_BIG;
-	w.blk_events = SP_LINES * ( width / 2 > 512 ? width / 2 : 512 );
+	w.blk_events = D.cap_blk_events;
 	w.view_events = (size_t)w.nbands * w.blk_events;
 	w.scanbits = nullptr; w.scanbits_words = ( w.max_cands + 32 ) / 32;
 	if( w.scanbits_words > SP_BITWORDS )
@@ -608,6 +631,48 @@ int ensure_batch( int nviews, int width, int height )
 	return 0;
 }
 
+/* after a batch: did a per-view capacity overflow?  Grow it from the counters (what the batch wanted, + 25 %) and tell
+ * the caller to render again.  Returns 1 = re-run, 0 = fine, -1 = a limit that cannot grow was hit */
+int check_capacities()
+{
+	const unsigned long long *c = D.h_counters;
+	const rc_scene_t &sc = D.sc;
+	int again = 0;
+	if( c[RC_CTR_OVERFLOW_STACK] || c[RC_CTR_OVERFLOW_CACHE] )
+	{
+		snprintf( D.err, sizeof( D.err ), "batch dropped work: %llu views past the BSP depth limit, %llu surface cache blocks past the luxel limit",
+			c[RC_CTR_OVERFLOW_STACK], c[RC_CTR_OVERFLOW_CACHE] );
+		return -1;
+	}
+	if( c[RC_CTR_OVERFLOW_CANDS] )
+	{
+		const int worst = sc.numsurfaces < 65000 ? sc.numsurfaces : 65000;
+		if( D.cap_cands >= worst ) { snprintf( D.err, sizeof( D.err ), "more than %d visible faces in a view", worst ); return -1; }
+		long long want = (long long)c[RC_CTR_MAX_CANDS] * 5 / 4 + 64;
+		D.cap_cands = (int)( want < worst ? want : worst );
+		if( D.cap_edges < 6 * D.cap_cands + 64 ) D.cap_edges = 6 * D.cap_cands + 64;
+		again = 1;
+	}
+	if( c[RC_CTR_OVERFLOW_EDGES] )
+	{
+		long long want = (long long)c[RC_CTR_MAX_EDGES] * 5 / 4 + 64;
+		if( want <= D.cap_edges ) want = (long long)D.cap_edges * 2;
+		if( want > 4000000 ) { snprintf( D.err, sizeof( D.err ), "more than 4M edges in a view" ); return -1; }
+		D.cap_edges = (int)want;
+		again = 1;
+	}
+	if( c[RC_CTR_OVERFLOW_EVENTS] )
+	{
+		long long want = (long long)c[RC_CTR_MAX_BAND_EVENTS] * 5 / 4 + 64;
+		if( want <= D.cap_blk_events ) want = (long long)D.cap_blk_events * 2;
+		if( want > ( 1 << 24 )) { snprintf( D.err, sizeof( D.err ), "more than 16M edge events in a band" ); return -1; }
+		D.cap_blk_events = (int)(( want + 31 ) & ~31ll );
+		again = 1;
+	}
+	if( again ) D.caps_dirty = true;
+	return again;
+}
+
 /* the device stages of one batch on D.stream; ev != NULL -> stage boundaries are recorded */
 /* the batch work record restricted to views [v0, v1): every per-view array starts at v0; slice k owns its own cache
  * work list, cursors and bit-set scratch so that slices can run on different streams at the same time */
@@ -618,7 +683,7 @@ rc_work_t make_slice( int k, int v0, int v1 )
 	const size_t nslots = (size_t)sc.numsurfaces * 4;
 	ws.nviews = v1 - v0;
 	ws.views += v0;
-	ws.walkstack += (size_t)v0 * ws.stack_ints;
+	ws.walkstack += (size_t)k * D.vw_grid * ws.stack_ints; /* per resident block of the slice's k_viswalk */
 	ws.cands += (size_t)v0 * ws.max_cands; ws.surfs += (size_t)v0 * ws.max_cands;
 	ws.edges += (size_t)v0 * ws.max_edges;
 	ws.ncands += v0; ws.nedges += v0;
@@ -645,7 +710,7 @@ int launch_slice( const rc_work_t &ws, int k, cudaStream_t st, cudaEvent_t *evs,
 	CK( cudaMemsetAsync( ws.cache_need, 0, sizeof( uint32_t ) * (( sc.numsurfaces * 4 + 31 ) / 32 + 1 ), st ));
 	CK( cudaMemsetAsync( ws.cache_nlist, 0, sizeof( int32_t ) * 8, st ));
 	if( evs ) CK( cudaEventRecord( evs[0], st ));
-	k_viswalk<VW_NTHREADS><<<ws.nviews, VW_NTHREADS, (size_t)ws.vis_smem, st>>>( sc, ws );
+	k_viswalk<VW_NTHREADS><<<ws.nviews < D.vw_grid ? ws.nviews : D.vw_grid, VW_NTHREADS, (size_t)ws.vis_smem, st>>>( sc, ws );
 	D.launches++;
 	if( evs ) CK( cudaEventRecord( evs[1], st ));
 	{
@@ -703,6 +768,7 @@ int run_batch( int nslices, int nstreams, bool timed, uint16_t *color_out, int16
 		if( launch_slice( ws, 0, st, timed ? D.ev : nullptr, true ) != 0 ) return -1;
 		if( color_out ) CK( cudaMemcpyAsync( color_out, w.color, (size_t)w.nviews * vpx * 2, cudaMemcpyDeviceToHost, st ));
 		if( z_out ) CK( cudaMemcpyAsync( z_out, w.zbuf, (size_t)w.nviews * vpx * 2, cudaMemcpyDeviceToHost, st ));
+		CK( cudaMemcpyAsync( D.h_counters, D.d_counters, sizeof( unsigned long long ) * RC_CTR_COUNT, cudaMemcpyDeviceToHost, st ));
 		CK( cudaGetLastError());
 		return 0;
 	}
@@ -725,6 +791,7 @@ int run_batch( int nslices, int nstreams, bool timed, uint16_t *color_out, int16
 		CK( cudaStreamWaitEvent( st, D.ev_slice[k], 0 ));
 	}
 	if( timed ) CK( cudaEventRecord( D.ev[RC_BENCH_STAGES], st ));
+	CK( cudaMemcpyAsync( D.h_counters, D.d_counters, sizeof( unsigned long long ) * RC_CTR_COUNT, cudaMemcpyDeviceToHost, st ));
 	CK( cudaGetLastError());
 	return 0;
 }
@@ -746,7 +813,9 @@ int rc_dev_init( int device )
 	cudaDeviceProp prop;
 	CK( cudaGetDeviceProperties( &prop, device ));
 	snprintf( D.name, sizeof( D.name ), "%s (sm_%d%d, %d SMs)", prop.name, prop.major, prop.minor, prop.multiProcessorCount );
-	D.device = device;
+	D.device = device; D.num_sms = prop.multiProcessorCount;
+	CK( cudaHostAlloc( (void **)&D.h_counters, sizeof( unsigned long long ) * RC_CTR_COUNT, cudaHostAllocDefault ));
+	memset( D.h_counters, 0, sizeof( unsigned long long ) * RC_CTR_COUNT );
 	CK( cudaStreamCreateWithFlags( &D.stream, cudaStreamNonBlocking ));
 	CK( cudaStreamCreateWithFlags( &D.copy, cudaStreamNonBlocking ));
 	for( auto &e : D.ev_slice ) CK( cudaEventCreateWithFlags( &e, cudaEventDisableTiming ));
@@ -779,6 +848,8 @@ void rc_dev_shutdown( void )
 		(void **)&D.d_counters, &D.d_flush };
 	for( void **p : ptrs ) { if( *p ) cudaFree( *p ); *p = nullptr; }
 	for( void *&p : D.d_scene ) { if( p ) cudaFree( p ); p = nullptr; }
+	if( D.h_counters ) { cudaFreeHost( D.h_counters ); D.h_counters = nullptr; }
+	D.cap_cands = D.cap_edges = D.cap_blk_events = 0; D.caps_dirty = false;
 	D.display_bytes = 0; D.ndlights = 0; D.screen_bpp = 0; D.cache_texels = 0; D.ntextures = 0;
 	D.sc = rc_scene_t{}; D.h_surfaces.clear(); D.h_textures.clear();
 	cudaStream_t *streams[] = { &D.stream, &D.copy };
@@ -796,6 +867,7 @@ void rc_dev_shutdown( void )
 const char *rc_dev_last_error( void ) { return D.err; }
 const char *rc_dev_name( void ) { return D.name; }
 uint64_t rc_dev_launch_count( void ) { return D.launches; }
+uint64_t rc_dev_h2d_bytes( int reset ) { const uint64_t v = D.h2d_bytes; if( reset ) D.h2d_bytes = 0; return v; }
 
 int rc_dev_upload_luts( const uint16_t *colormap, const uint16_t *lightgamma, const int32_t *sintable )
 {
@@ -821,6 +893,7 @@ int rc_dev_upload_scene( const rc_scene_t *sc, size_t cache_texels )
 {
 	CK( cudaStreamSynchronize( D.stream ));
 	free_batch();
+	D.cap_cands = D.cap_edges = D.cap_blk_events = 0; D.caps_dirty = false;
 	rc_scene_t d = *sc;
 	rc_plane_t *planes = (rc_plane_t *)D.d_scene[0]; rc_node_t *nodes = (rc_node_t *)D.d_scene[1];
 	rc_leaf_t *leafs = (rc_leaf_t *)D.d_scene[2]; rc_surface_t *surfaces = (rc_surface_t *)D.d_scene[3];
@@ -933,6 +1006,7 @@ int rc_dev_set_lightstyles( const int32_t *values )
 	memcpy( D.h_styles, values, sizeof( D.h_styles ));
 	CK( cudaStreamSynchronize( D.stream ));
 	CK( cudaMemcpy( D.d_styles, D.h_styles, sizeof( D.h_styles ), cudaMemcpyHostToDevice ));
+	D.h2d_bytes += sizeof( D.h_styles );
 	return 0;
 }
 
@@ -948,6 +1022,7 @@ int rc_dev_set_dlights( const rc_dlight_t *lights, int n )
 	CK( cudaStreamSynchronize( D.stream ));
 	if( !D.d_dlights && dalloc( &D.d_dlights, RC_MAX_DLIGHTS ) != 0 ) return -1;
 	CK( cudaMemcpyAsync( D.d_dlights, lights, sizeof( rc_dlight_t ) * n, cudaMemcpyHostToDevice, D.stream ));
+	D.h2d_bytes += sizeof( rc_dlight_t ) * (size_t)n;
 	k_dlight_mark<<<( D.sc.numsurfaces + 127 ) / 128, 128, 0, D.stream>>>( D.sc, D.d_dlights, n, D.d_dlightbits );
 	D.launches++;
 	CK( cudaGetLastError());
@@ -970,37 +1045,45 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 	if( !D.ready ) { snprintf( D.err, sizeof( D.err ), "device not initialised" ); return -1; }
 	if( !D.sc.numsurfaces || !D.sc.surfaces ) { snprintf( D.err, sizeof( D.err ), "no world uploaded" ); return -1; }
 	if( nviews <= 0 || width <= 0 || height <= 0 || height > 1200 ) { snprintf( D.err, sizeof( D.err ), "bad batch geometry" ); return -1; }
-	if( ensure_batch( nviews, width, height ) != 0 ) return -1;
-	rc_work_t &w = D.w;
-	w.nviews = nviews; w.clear = clear;
-	cudaStream_t st = D.stream;
-	CK( cudaMemcpyAsync( D.d_views, views, sizeof( rc_view_t ) * nviews, cudaMemcpyHostToDevice, st ));
-	size_t px = (size_t)nviews * width * height;
-	if( clear )
+	for( int attempt = 0; ; attempt++ )
 	{
-		/* views that do not cover the whole buffer leave a border the span pass never touches */
-		bool full = true;
-		for( int i = 0; i < nviews && full; i++ )
-			full = views[i].vrect[0] == 0 && views[i].vrect[1] == 0 && views[i].vrect[2] == width && views[i].vrect[3] == height;
-		if( !full )
+		if( ensure_batch( nviews, width, height ) != 0 ) return -1;
+		rc_work_t &w = D.w;
+		w.nviews = nviews; w.clear = clear;
+		cudaStream_t st = D.stream;
+		CK( cudaMemcpyAsync( D.d_views, views, sizeof( rc_view_t ) * nviews, cudaMemcpyHostToDevice, st ));
+		D.h2d_bytes += sizeof( rc_view_t ) * (size_t)nviews;
+		size_t px = (size_t)nviews * width * height;
+		if( clear )
 		{
-			CK( cudaMemsetAsync( w.color, 0, px * 2, st ));
-			CK( cudaMemsetAsync( w.zbuf, 0, px * 2, st ));
+			/* views that do not cover the whole buffer leave a border the span pass never touches */
+			bool full = true;
+			for( int i = 0; i < nviews && full; i++ )
+				full = views[i].vrect[0] == 0 && views[i].vrect[1] == 0 && views[i].vrect[2] == width && views[i].vrect[3] == height;
+			if( !full )
+			{
+				CK( cudaMemsetAsync( w.color, 0, px * 2, st ));
+				CK( cudaMemsetAsync( w.zbuf, 0, px * 2, st ));
+			}
 		}
+		{
+			/* frames that go back to the host: 4 slices of views on two streams, so that the copies of the first pair
+			 * overlap the stages of the second (the copies are the long pole: PCIe).  Frames that stay in HBM: one
+			 * stream - running the slices side by side was measured and gains nothing (every kernel already exposes the
+			 * whole batch's parallelism; the slices move in lockstep) */
+			const bool out = color_out || z_out;
+			const int nslices = out && nviews >= 16 * RC_MAX_SLICES ? RC_MAX_SLICES : 1;
+			if( run_batch( nslices, 2, false, color_out, z_out ) != 0 ) return -1;
+			if( out && nslices > 1 ) CK( cudaStreamSynchronize( D.copy ));
+		}
+		CK( cudaStreamSynchronize( st ));
+		D.have_batch = true;
+		/* a per-view capacity overflowed: nothing of this batch is trusted - grow it and render again */
+		const int again = check_capacities();
+		if( again < 0 ) return -1;
+		if( !again ) return 0;
+		if( attempt >= 6 ) { snprintf( D.err, sizeof( D.err ), "capacities still overflow after %d attempts", attempt + 1 ); return -1; }
 	}
-	{
-		/* frames that go back to the host: 4 slices of views on two streams, so that the copies of the first pair
-		 * overlap the stages of the second (the copies are the long pole: PCIe).  Frames that stay in HBM: one
-		 * stream - running the slices side by side was measured and gains nothing (every kernel already exposes the
-		 * whole batch's parallelism; the slices move in lockstep) */
-		const bool out = color_out || z_out;
-		const int nslices = out && nviews >= 16 * RC_MAX_SLICES ? RC_MAX_SLICES : 1;
-		if( run_batch( nslices, 2, false, color_out, z_out ) != 0 ) return -1;
-		if( out && nslices > 1 ) CK( cudaStreamSynchronize( D.copy ));
-	}
-	CK( cudaStreamSynchronize( st ));
-	D.have_batch = true;
-	return 0;
 }
 
 int rc_dev_bench_resident( int iters, int flags, float *ms_total, float *ms_stage )

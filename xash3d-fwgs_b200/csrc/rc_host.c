@@ -95,6 +95,7 @@ static struct
 	int          had_dlights;
 	uint         sw_stride, sw_bpp, sw_r, sw_g, sw_b;
 	uint         map_valid, map_bpp, map_r, map_g, map_b; /* display format the device's screen map was built for */
+	unsigned long long last_h2d;
 	char         error[512];
 } rc;
 
@@ -910,12 +911,14 @@ int RefCuda_RenderViews( const ref_viewpass_t *views, int nviews, unsigned short
 {
 	if( !rc.initialized || nviews <= 0 )
 		return -1;
+	rc_dev_h2d_bytes( 1 );
 	rc_prepare_batch();
 	rc.nviews = 0;
 	for( int i = 0; i < nviews; i++ )
 		rc_queue_view( &views[i] );
 	int r = rc_dev_render( rc.views, rc.nviews, gpGlobals->width, gpGlobals->height, clear, color_out, z_out );
 	rc.nviews = 0;
+	rc.last_h2d = rc_dev_h2d_bytes( 0 );
 	if( r != 0 )
 		gEngfuncs.Host_Error( "ref_cuda: rc_dev_render failed: %s\n", rc_dev_last_error());
 	return r;
@@ -940,6 +943,7 @@ int RefCuda_BlitViews( int first, int nviews, void *dst, unsigned int stride, un
 
 int RefCuda_GetCounters( unsigned long long *out, int n ) { return rc_dev_read_counters((uint64_t *)out, n ); }
 unsigned long long RefCuda_LaunchCount( void ) { return rc_dev_launch_count(); }
+unsigned long long RefCuda_BatchH2DBytes( void ) { return rc.last_h2d; }
 const char *RefCuda_DeviceName( void ) { return rc_dev_name(); }
 
 /* ---------------------------------------------------------------------------------------------- */

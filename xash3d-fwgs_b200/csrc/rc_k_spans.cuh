@@ -74,6 +74,7 @@ __global__ void __launch_bounds__( EV_THREADS ) k_events( rc_work_t w )
 	const bool valid = y >= y0 && y < y0 + vw_h && y < w.height;
 
 	const int32_t nview = min( w.nedges[view], w.max_edges );
+	if( t == 0 && blockIdx.y == 0 ) atomicMax( &w.counters[RC_CTR_MAX_EDGES], (unsigned long long)w.nedges[view] );
 	const rc_edge_t *vedges = w.edges + (size_t)view * w.max_edges;
 	unsigned long long *arena = w.events + ((size_t)view * nbands + band ) * w.blk_events;
 	const int32_t bmwords = ( w.ncands[view] + 32 ) >> 5; /* surface numbers are candidate index + 1 */
@@ -252,6 +253,7 @@ __global__ void __launch_bounds__( EV_THREADS ) k_events( rc_work_t w )
 	const bool fits = off + n + 1 <= w.blk_events;
 	if( warp == 0 )
 	{
+		if( lane == 31 ) atomicMax( &w.counters[RC_CTR_MAX_BAND_EVENTS], (unsigned long long)incl );
 		rc_lineinfo_t li;
 		li.ofs = -1; li.nsp = 0;
 		if( valid && fits )
@@ -614,15 +616,15 @@ __global__ void __launch_bounds__( LN_WARPS * 32, 8 ) k_lines( rc_work_t w )
 		if( lane == 0 )
 		{
 			const long long dbg2 = clock64();
-			atomicAdd( &w.counters[16], (unsigned long long)( dbg1 - dbg0 )); atomicMax( &w.counters[17], (unsigned long long)( dbg1 - dbg0 ));
-			atomicAdd( &w.counters[18], (unsigned long long)( dbg2 - dbg1 )); atomicMax( &w.counters[19], (unsigned long long)( dbg2 - dbg1 ));
+			atomicAdd( &w.counters[26], (unsigned long long)( dbg1 - dbg0 )); atomicMax( &w.counters[27], (unsigned long long)( dbg1 - dbg0 ));
+			atomicAdd( &w.counters[28], (unsigned long long)( dbg2 - dbg1 )); atomicMax( &w.counters[29], (unsigned long long)( dbg2 - dbg1 ));
 			atomicAdd( &w.counters[24], (unsigned long long)n ); atomicMax( &w.counters[25], (unsigned long long)n );
-			atomicAdd( &w.counters[20], 1ull );
+			atomicAdd( &w.counters[30], 1ull );
 		}
 #endif
 	}
 #ifdef RC_SPANS_DEBUG
-	if( lane == 0 ) atomicMax( &w.counters[21], (unsigned long long)( clock64() - dbg_start ));
+	if( lane == 0 ) atomicMax( &w.counters[31], (unsigned long long)( clock64() - dbg_start ));
 #endif
 	if( lane == 0 )
 	{

@@ -128,16 +128,13 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 	__shared__ int32_t s_warp[VW_THREADS / 32];
 	__shared__ rc_view_t s_view;
 
-	const int view = blockIdx.x, t = threadIdx.x, lane = t & 31, warp = t >> 5;
+	const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
 #ifdef RC_SPANS_DEBUG
 	long long dbg_t[10]; int dbg_n = 0;
 #define VW_MARK() do { __syncthreads(); dbg_t[dbg_n++] = clock64(); } while( 0 )
 #else
 #define VW_MARK() do { } while( 0 )
 #endif
-	VW_MARK();
-	if( t < (int)( sizeof( rc_view_t ) / 4 ))
-		reinterpret_cast<uint32_t *>( &s_view )[t] = reinterpret_cast<const uint32_t *>( &w.views[view] )[t];
 	const rc_view_t *vw = &s_view;
 	const int32_t viswords = w.visbytes_padded >> 2;
 	uint32_t *vis = s_bits;
@@ -147,7 +144,8 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 	const int32_t allwords = viswords + w.nodewords + w.leafwords + w.surfwords;
 
 	const int32_t cap = 2 * sc.numnodes + 2;
-	int32_t *scr = w.walkstack + (size_t)view * w.stack_ints;
+	/* the block is persistent over views (grid = resident blocks): the tree is staged and the scratch set up once */
+	int32_t *scr = w.walkstack + (size_t)blockIdx.x * w.stack_ints;
 	const uint16_t *sn16 = nullptr, *mk16 = nullptr;
 	{
 		unsigned char *p = reinterpret_cast<unsigned char *>( s_bits ) + (((size_t)allwords * 4 + 15 ) & ~(size_t)15 );
@@ -179,6 +177,15 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 	int32_t *nodepos = scr + 8 * (size_t)cap;
 	int32_t *nflag = nodepos + sc.numnodes + 8, *lflag = nflag + sc.numnodes;
 
+	for( int view = blockIdx.x; view < w.nviews; view += gridDim.x )
+	{
+#ifdef RC_SPANS_DEBUG
+	dbg_n = 0;
+#endif
+	__syncthreads(); /* the previous view is done with s_view and the scratch */
+	VW_MARK();
+	if( t < (int)( sizeof( rc_view_t ) / 4 ))
+		reinterpret_cast<uint32_t *>( &s_view )[t] = reinterpret_cast<const uint32_t *>( &w.views[view] )[t];
 	for( int i = t; i < allwords; i += VW_THREADS ) s_bits[i] = 0;
 	for( int i = t; i < sc.numnodes; i += VW_THREADS ) nodepos[i] = -1; /* not visited: precedes no leaf */
 	__syncthreads();
@@ -505,7 +512,9 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 		atomicAdd( &w.counters[RC_CTR_PIXELS], (unsigned long long)vw->vrect[2] * vw->vrect[3] );
 		if( s_ovf ) atomicAdd( &w.counters[RC_CTR_OVERFLOW_STACK], 1ull );
 		if( total > w.max_cands ) atomicAdd( &w.counters[RC_CTR_OVERFLOW_CANDS], 1ull );
+		atomicMax( &w.counters[RC_CTR_MAX_CANDS], (unsigned long long)total );
 	}
+	} /* views */
 }
 
 #endif /* RC_K_VIS_CUH */

@@ -16,7 +16,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_HERE)
 HOST_LIB_PATH = os.path.join(_HERE, "libxashhost.so")
-REF_CUDA_PATH = os.environ.get("REF_CUDA_LIB") or os.path.join(_HERE, "libref_cuda.so")  # override: development aid
+REF_CUDA_PATH = os.path.join(_HERE, "libref_cuda.so")
 REF_SOFT_PATH = os.path.join(_ROOT, "oracle", "_ref", "libref_soft.so")
 
 RF_DRAW_WORLD = 1

@@ -42,13 +42,14 @@ CTR_NAMES = ["views", "pixels", "cands", "surfs", "edges", "spans", "cache_block
 def make_map(which: str = "small", ncameras: int = 256, **kw):
     """Named synthetic worlds of BASELINE.json: tiny (unit tests), small (Map S: C1/C2/C5), large (Map L: C3)."""
     spec = {"tiny": mapgen.spec_tiny, "small": mapgen.spec_small, "medium": mapgen.spec_medium, "large": mapgen.spec_large}[which](**kw)
-    return mapgen.generate(spec, ncameras=ncameras)
+    return mapgen.generate_cached(spec, ncameras=ncameras)
 
 
 class Renderer:
     def __init__(self, ref_path: str, width: int, height: int, gmap=None, cvars: dict | None = None, sw_format=None):
-        self.is_cuda = ref_path == REF_CUDA_PATH or ref_path.endswith("libref_cuda.so") or ref_path.endswith("libref_cuda_emu.so")
         self.host = Host(ref_path, width, height, cvars, sw_format)
+        # the batch extension (include/ref_cuda.h) is what makes a plugin drivable in batches; ref_soft has none
+        self.is_cuda = bool(self.host.symbol("RefCuda_RenderViews"))
         self.width, self.height = width, height
         L = self.host.lib
         L.xh_soft_render_views.restype = C.c_double
@@ -61,6 +62,7 @@ class Renderer:
             self._counters = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int)(sym("RefCuda_GetCounters"))
             self._launches = C.CFUNCTYPE(C.c_ulonglong)(sym("RefCuda_LaunchCount"))
             self._devname = C.CFUNCTYPE(C.c_char_p)(sym("RefCuda_DeviceName"))
+            self._h2d = C.CFUNCTYPE(C.c_ulonglong)(sym("RefCuda_BatchH2DBytes"))
             self._blit = C.CFUNCTYPE(C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.POINTER(C.c_float))(sym("RefCuda_BlitViews"))
         if gmap is not None:
             self.load_map(gmap)
@@ -205,6 +207,10 @@ class Renderer:
         a = np.zeros(32, np.uint64)
         self._counters(a.ctypes.data, 32)
         return dict(zip(CTR_NAMES, [int(x) for x in a[: len(CTR_NAMES)]]))
+
+    def batch_h2d_bytes(self) -> int:
+        """host->device bytes the last RefCuda_RenderViews call uploaded (per-view constants, light styles, entity state)"""
+        return int(self._h2d())
 
     def launch_count(self) -> int:
         return int(self._launches())

@@ -140,6 +140,7 @@ class MapSpec:
     extra_styles_prob: tuple = (0, 1)  # faces that get light styles 1..3 in addition to 0 (C3)
     ntextures: int = 16
     name: str = "synth"
+    novis: bool = False  # no visibility lump: every leaf's visofs is -1
 
 
 @dataclass
@@ -150,6 +151,7 @@ class GeneratedMap:
     cameras: np.ndarray = field(default_factory=lambda: np.zeros((0, 6), np.float32))  # x y z pitch yaw roll
     grid: np.ndarray | None = None
     origin: tuple = (0, 0, 0)
+    extras: dict | None = None  # what the generator placed besides the world: brush submodels, sprite / model spots
 
 
 def _carve(spec: MapSpec):
@@ -532,15 +534,22 @@ def generate(spec: MapSpec = MapSpec(), ncameras: int = 256) -> GeneratedMap:
             ta = int(np.flatnonzero(np.array(tv[:3]))[0])
             W[..., sa] = S * sv[sa]
             W[..., ta] = T * tv[ta]
-            d2 = ((W[:, :, None, :] - lights_a[None, None, :, :3]) ** 2).sum(-1)
-            contrib = lights_a[None, None, :, 3] / (1.0 + d2 / (140.0**2))
+            # lights further than the cut-off radius add exactly 0; on big maps only the ones that can reach the
+            # face are summed (small maps keep the full sum: their bytes are pinned by committed goldens)
+            la = lights_a
+            if len(lights_a) > 100:
+                wmin, wmax = W.reshape(-1, 3).min(0), W.reshape(-1, 3).max(0)
+                gap = np.maximum(np.maximum(wmin[None, :] - lights_a[:, :3], lights_a[:, :3] - wmax[None, :]), 0.0)
+                la = lights_a[(gap**2).sum(-1) < (6 * CELL * 1.5) ** 2]
+            d2 = ((W[:, :, None, :] - la[None, None, :, :3]) ** 2).sum(-1)
+            contrib = la[None, None, :, 3] / (1.0 + d2 / (140.0**2))
             near = d2 < (6 * CELL * 1.5) ** 2
             contrib = contrib * near
             lightofs = len(light_blob)
             for si in range(nstyles):
                 rgb = np.zeros((th, sw, 3))
                 for ch in range(3):
-                    tint = 1.0 - 0.35 * (lights_a[None, None, :, 4] == ch)
+                    tint = 1.0 - 0.35 * (la[None, None, :, 4] == ch)
                     rgb[..., ch] = (contrib * tint).sum(-1)
                 noise = (_hash_u32(S.astype(np.int64), T.astype(np.int64), np.int64(fi * 4 + si)) & 0x1F).astype(np.float64)
                 amb = 18.0 if si == 0 else 0.0
@@ -569,6 +578,8 @@ def generate(spec: MapSpec = MapSpec(), ncameras: int = 256) -> GeneratedMap:
     vis_blob = bytearray()
     visofs = [-1] * nleafs
     for li in range(1, nleafs):
+        if spec.novis:
+            break
         visofs[li] = len(vis_blob)
         vis_blob += _rle(vis_rows[li - 1])
 
@@ -608,7 +619,7 @@ def generate(spec: MapSpec = MapSpec(), ncameras: int = 256) -> GeneratedMap:
     wmins = [b.world(a, 0) for a in range(3)]
     wmaxs = [b.world(a, g.shape[a]) for a in range(3)]
     L[14] = struct.pack("<9f4i3i", *map(float, wmins), *map(float, wmaxs), 0.0, 0.0, 0.0, 0, 0, 0, 0, nvis, 0, len(face_recs))
-    assert len(verts) < 65536 and len(edges) < 65536 and len(face_recs) < 65536 and len(marks) < 65536 and len(b.nodes) < 32768 and nleafs < 32768
+    assert len(verts) < 65536 and len(face_recs) < 65536 and len(marks) < 65536 and len(b.nodes) < 32768 and nleafs < 32768
     out = bytearray(struct.pack("<i", 30) + b"\0" * (8 * 15))
     for i in range(15):
         while len(out) % 4:
@@ -616,7 +627,7 @@ def generate(spec: MapSpec = MapSpec(), ncameras: int = 256) -> GeneratedMap:
         struct.pack_into("<ii", out, 4 + 8 * i, len(out), len(L[i]))
         out += L[i]
 
-    cams = _cameras(b, g, spec, ncameras)
+    cams = _cameras(b.org, g, spec, ncameras)
     stats = dict(
         faces=len(face_recs), nodes=len(b.nodes), leafs=nleafs, planes=len(b.planes), verts=len(verts), edges=len(edges),
         marksurfaces=len(marks), textures=nt, lightbytes=len(light_blob), visbytes_row=(nvis + 7) // 8, vislump=len(vis_blob),
@@ -626,18 +637,23 @@ def generate(spec: MapSpec = MapSpec(), ncameras: int = 256) -> GeneratedMap:
 
 
 def _rle(row: np.ndarray) -> bytes:
+    """Zero-run RLE of a PVS row (Mod_DecompressPVS's inverse): non-zero bytes verbatim, runs of zeros as {0, count <= 255}."""
+    row = np.asarray(row, dtype=np.uint8)
+    n = len(row)
+    if not n:
+        return b""
+    nz = (row != 0).astype(np.int8)
+    cuts = np.concatenate(([0], np.flatnonzero(np.diff(nz)) + 1, [n]))
     out = bytearray()
-    i, n = 0, len(row)
-    while i < n:
-        v = int(row[i])
-        out.append(v)
-        i += 1
-        if v == 0:
-            rep = 1
-            while i < n and rep < 255 and row[i] == 0:
-                rep += 1
-                i += 1
-            out.append(rep)
+    raw = row.tobytes()
+    for a, c in zip(cuts[:-1].tolist(), cuts[1:].tolist()):
+        if raw[a]:
+            out += raw[a:c]
+        else:
+            full, rem = divmod(c - a, 255)
+            out += b"\x00\xff" * full
+            if rem:
+                out += bytes((0, rem))
     return bytes(out)
 
 
@@ -653,52 +669,52 @@ def _compute_pvs(b: _Builder, g, zone, nzones, nvis):
         for z0, z1 in set(zip(pa.tolist(), pb.tolist())):
             adj[z0].setdefault((axis, 1), set()).add(z1)
             adj[z1].setdefault((axis, -1), set()).add(z0)
-    zvis = np.zeros((nzones, nzones), dtype=bool)
-    for z in range(nzones):
-        seen = {(z, (0, 0, 0))}
-        stack = [(z, (0, 0, 0))]
-        zvis[z, z] = True
-        while stack:
-            cur, sg = stack.pop()
-            for (axis, d), nbrs in adj[cur].items():
-                if sg[axis] not in (0, d):
-                    continue
-                ns = list(sg)
-                ns[axis] = d
-                ns = tuple(ns)
-                for nb in nbrs:
-                    if (nb, ns) not in seen:
-                        seen.add((nb, ns))
-                        zvis[z, nb] = True
-                        stack.append((nb, ns))
+    # a path is valid iff along every axis all its moves go the same way <=> all moves lie in one of the 8 octants:
+    # per octant the reachable set is plain graph reachability over that octant's directed edges
+    from scipy.sparse import csr_matrix
+    from scipy.sparse.csgraph import shortest_path
+
+    zvis = np.eye(nzones, dtype=bool)
+    for octant in range(8):
+        rows, cols = [], []
+        for axis in range(3):
+            d = 1 if (octant >> axis) & 1 else -1
+            for z0 in range(nzones):
+                nb = adj[z0].get((axis, d))
+                if nb:
+                    rows.extend([z0] * len(nb))
+                    cols.extend(nb)
+        if not rows:
+            continue
+        a = csr_matrix((np.ones(len(rows), dtype=np.int8), (rows, cols)), shape=(nzones, nzones))
+        for lo in range(0, nzones, 1024):  # blocks of sources bound the dense distance matrix
+            idx = np.arange(lo, min(nzones, lo + 1024))
+            dist = shortest_path(a, method="D", directed=True, unweighted=True, indices=idx)
+            zvis[idx] |= np.isfinite(dist)
     # leaf -> zones
     nleafs = len(b.leafs)
-    leaf_zones = [None] * nleafs
-    zl = np.zeros((nzones, nleafs), dtype=bool)
+    lr, lc = [], []
     for li in range(1, nleafs):
         x0, x1, y0, y1, z0, z1 = b.leafs[li]["box"]
         zs = np.unique(zone[x0:x1, y0:y1, z0:z1])
         zs = zs[zs >= 0]
-        leaf_zones[li] = zs
-        zl[zs, li] = True
-    rows = []
+        lr.extend([li] * len(zs))
+        lc.extend(zs.tolist())
+    lz = csr_matrix((np.ones(len(lr), dtype=np.float32), (lr, lc)), shape=(nleafs, nzones))
     nbytes = (nvis + 7) // 8
-    for li in range(1, nleafs):
-        zs = leaf_zones[li]
-        if len(zs) == 0:
-            vis_leaves = np.zeros(nleafs, dtype=bool)
-            vis_leaves[li] = True
-        else:
-            vz = zvis[zs].any(axis=0)
-            vis_leaves = zl[vz].any(axis=0)
-            vis_leaves[li] = True
-        bits = vis_leaves[1:]
-        row = np.packbits(bits, bitorder="little")
-        rows.append(row[:nbytes])
+    rows = []
+    lzt = lz.T.tocsr()
+    for lo in range(1, nleafs, 2048):
+        hi = min(nleafs, lo + 2048)
+        seen_z = lz[lo:hi] @ zvis.astype(np.float32)  # [leaf, zone]: zones the leaf's zones see
+        vis = (csr_matrix(seen_z > 0, dtype=np.float32) @ lzt).toarray() > 0  # [leaf, leaf]
+        vis[np.arange(hi - lo), np.arange(lo, hi)] = True
+        packed = np.packbits(vis[:, 1:], axis=1, bitorder="little")
+        rows.extend(packed[i, :nbytes] for i in range(hi - lo))
     return rows
 
 
-def _cameras(b: _Builder, g, spec: MapSpec, n: int):
+def _cameras(org, g, spec: MapSpec, n: int):
     """Eye points inside empty space, >= 1 cell from any wall sideways; yaw U[0,360), pitch U[-30,30]."""
     rng = LCG(spec.seed ^ 0xCA3E7A)
     cams = []
@@ -712,9 +728,9 @@ def _cameras(b: _Builder, g, spec: MapSpec, n: int):
         z = k * cz + 2  # second cell above the floor ~ eye height 48..64
         if not (g[x - 1 : x + 2, y - 1 : y + 2, z] == EMPTY).all():
             continue
-        px = b.world(0, x) + rng.uniform(4, CELL - 4)
-        py = b.world(1, y) + rng.uniform(4, CELL - 4)
-        pz = b.world(2, z) + rng.uniform(4, CELL - 4)
+        px = org[0] + x * CELL + rng.uniform(4, CELL - 4)
+        py = org[1] + y * CELL + rng.uniform(4, CELL - 4)
+        pz = org[2] + z * CELL + rng.uniform(4, CELL - 4)
         cams.append((px, py, pz, rng.uniform(-30, 30), rng.uniform(0, 360), 0.0))
     return np.array(cams, dtype=np.float32)
 
@@ -740,8 +756,44 @@ def spec_medium(seed=0xB203, **kw) -> MapSpec:
 
 
 def spec_large(seed=0xB203, **kw) -> MapSpec:
-    """Map L: 24x24x4 rooms, ~30k faces, extra light styles on 25% of faces (C3)."""
-    return MapSpec(rooms=(24, 24, 4), seed=seed, name="synth_l", extra_styles_prob=(1, 4), **kw)
+    """Map L: ~30k faces, extra light styles 1..11 on 25% of faces (C3).  16x16x4 rooms: the 24x24x4 grid SURVEY.md
+    pencilled in gives ~66k faces / ~100k vertices with this room generator, past BSP30's 16-bit vertex and
+    marksurface indices (common/bspfile.h:214-222); BASELINE.json states the face count, and this grid has it."""
+    kw.setdefault("extra_styles_prob", (1, 4))
+    return MapSpec(rooms=(16, 16, 4), seed=seed, name="synth_l", **kw)
+
+
+def generate_cached(spec: MapSpec = MapSpec(), ncameras: int = 256, cache_dir: str | None = None) -> GeneratedMap:
+    """generate() behind a disk cache keyed by the spec and this file's own bytes (big maps take a minute to build;
+    the cache directory is git-ignored and travels with the tree to the GPU box)."""
+    import hashlib
+    import os
+    import pickle
+
+    cache_dir = cache_dir or os.path.join(os.path.dirname(os.path.abspath(__file__)), "_mapcache")
+    with open(os.path.abspath(__file__), "rb") as f:
+        key = hashlib.sha256(f.read() + repr(spec).encode()).hexdigest()[:20]
+    path = os.path.join(cache_dir, f"{spec.name}_{key}.pkl")
+    if os.path.exists(path):
+        try:
+            with open(path, "rb") as f:
+                bsp, stats, grid, origin, extras = pickle.load(f)
+            gm = GeneratedMap(bsp, spec, stats, _cameras(origin, grid, spec, ncameras), grid, origin)
+            gm.extras = extras
+            return gm
+        except Exception:
+            pass
+    gm = generate(spec, ncameras)
+    if len(gm.bsp) > (1 << 20):  # small maps generate in a second or two
+        try:
+            os.makedirs(cache_dir, exist_ok=True)
+            tmp = path + f".{os.getpid()}.tmp"
+            with open(tmp, "wb") as f:
+                pickle.dump((gm.bsp, gm.stats, gm.grid, gm.origin, getattr(gm, "extras", None)), f)
+            os.replace(tmp, path)
+        except OSError:
+            pass
+    return gm
 
 
 if __name__ == "__main__":
