@@ -25,7 +25,7 @@ struct Emu
 	std::vector<rc_surface_t> surfaces; std::vector<int32_t> marks, surfedges; std::vector<uint16_t> edges;
 	std::vector<float> verts; std::vector<uint8_t> visdata, lightdata;
 	std::vector<rc_texture_t> textures; std::vector<uint16_t> texels, colormap, lightgamma, cache;
-	std::vector<int32_t> sintable;
+	std::vector<int32_t> sintable, sedgepartner; std::vector<float> sedgeverts;
 	int32_t styles[256];
 	struct Key { int32_t texnum; int32_t light[4]; bool valid; };
 	std::vector<Key> cachekey;
@@ -44,6 +44,7 @@ void fix_pointers()
 	E.sc.colormap = E.colormap.data(); E.sc.lightgamma = E.lightgamma.data(); E.sc.sintable = E.sintable.data();
 	E.sc.cache = E.cache.data();
 	E.sc.numtextures = (int32_t)E.textures.size();
+	E.sc.sedgeverts = E.sedgeverts.empty() ? nullptr : E.sedgeverts.data(); E.sc.sedgepartner = E.sedgepartner.empty() ? nullptr : E.sedgepartner.data();
 }
 
 void build_block( int s, int mip )
@@ -118,6 +119,9 @@ int rc_dev_upload_scene( const rc_scene_t *sc, size_t cache_texels )
 	E.cache.assign( cache_texels, 0 );
 	E.cachekey.assign( (size_t)sc->numsurfaces * 4, Emu::Key{} );
 	fix_pointers();
+	E.sedgeverts.assign( (size_t)sc->numsurfedges * 6 + 6, 0.0f ); E.sedgepartner.assign( (size_t)sc->numsurfedges + 1, -1 );
+	rc_build_sedge_tables( &E.sc, E.sedgeverts.data(), E.sedgepartner.data());
+	fix_pointers();
 	return 0;
 }
 
@@ -163,13 +167,15 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 		E.counters[RC_CTR_CANDS] += ncands;
 		/* A3 + A5 */
 		std::vector<rc_surf_t> surfs( ncands + 1 );
+		std::vector<uint16_t> candof( sc->numsurfaces + 2, 0 );
+		for( int ci = 0; ci < ncands; ci++ ) candof[cands[ci].surf] = (uint16_t)( ci + 1 );
 		std::vector<rc_edge_t> edges;
 		for( int ci = 0; ci < ncands; ci++ )
 		{
 			rc_edge_t local[256];
 			rc_facestate_t fs; memset( &fs, 0, sizeof( fs ));
 			fs.out = local; fs.maxout = 256; fs.surfnum = ci + 1;
-			rc_render_face( sc, vw, &cands[ci], &fs, &surfs[ci] );
+			rc_render_face( sc, vw, &cands[ci], &fs, &surfs[ci], cands.data(), candof.data(), ci );
 			for( int k = 0; k < fs.nout && k < 256; k++ ) edges.push_back( local[k] );
 			if( surfs[ci].emitted )
 			{

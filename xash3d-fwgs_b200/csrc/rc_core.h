@@ -14,6 +14,8 @@
 #define RC_CORE_H
 
 #include "rc_shared.h"
+#include <stdlib.h>
+#include <math.h>
 
 #if defined( __CUDACC__ )
 #define RC_HD __host__ __device__ __forceinline__
@@ -282,6 +284,65 @@ RC_HD int32_t rc_walk_world( const rc_scene_t *sc, const rc_view_t *vw, const ui
 /* ------------------------------------------------------------------------------------------ */
 /* A3: R_RenderFace / R_ClipEdge / R_EmitEdge (ref/soft/r_rast.c:63-584)                        */
 
+/* derived per-surfedge tables (built once per map on the host): both vertices of every surfedge in winding order
+ * (sv[numsurfedges][6]) and the other face that lists the same medge (partner[numsurfedges], see rc_scene_t) */
+static inline void rc_build_sedge_tables( const rc_scene_t *sc, float *sv, int32_t *partner )
+{
+	for( int32_t i = 0; i < sc->numsurfedges; i++ )
+	{
+		partner[i] = -1;
+		for( int k = 0; k < 6; k++ ) sv[(size_t)i * 6 + k] = 0.0f;
+		int32_t l = sc->surfedges[i];
+		const int a = l > 0 ? 0 : 1;
+		if( l < 0 ) l = -l;
+		if( l >= sc->numedges ) continue;
+		const int32_t i0 = sc->edges[2 * l + a], i1 = sc->edges[2 * l + ( a ^ 1 )];
+		if( i0 >= sc->numverts || i1 >= sc->numverts ) continue;
+		for( int k = 0; k < 3; k++ )
+		{
+			sv[(size_t)i * 6 + k] = sc->verts[3 * i0 + k];
+			sv[(size_t)i * 6 + 3 + k] = sc->verts[3 * i1 + k];
+		}
+	}
+	/* first and second user of every medge, in face order */
+	int32_t *user = (int32_t *)malloc( sizeof( int32_t ) * 2 * (size_t)( sc->numedges > 0 ? sc->numedges : 1 ));
+	if( !user ) return;
+	for( int32_t e = 0; e < 2 * sc->numedges; e++ ) user[e] = -1;
+	for( int32_t s = 0; s < sc->numsurfaces; s++ )
+		for( int32_t k = 0; k < sc->surfaces[s].numedges; k++ )
+		{
+			const int32_t se = sc->surfaces[s].firstedge + k;
+			if( se < 0 || se >= sc->numsurfedges ) continue;
+			int32_t l = sc->surfedges[se];
+			if( l < 0 ) l = -l;
+			if( l <= 0 || l >= sc->numedges ) continue;
+			if( user[2 * l] < 0 ) user[2 * l] = se;
+			else if( user[2 * l + 1] < 0 ) user[2 * l + 1] = se;
+		}
+	/* surfedge -> owning face */
+	int32_t *owner = (int32_t *)malloc( sizeof( int32_t ) * (size_t)( sc->numsurfedges > 0 ? sc->numsurfedges : 1 ));
+	if( owner )
+	{
+		for( int32_t i = 0; i < sc->numsurfedges; i++ ) owner[i] = -1;
+		for( int32_t s = 0; s < sc->numsurfaces; s++ )
+			for( int32_t k = 0; k < sc->surfaces[s].numedges; k++ )
+			{
+				const int32_t se = sc->surfaces[s].firstedge + k;
+				if( se >= 0 && se < sc->numsurfedges ) owner[se] = s;
+			}
+		for( int32_t l = 1; l < sc->numedges; l++ )
+		{
+			const int32_t sa = user[2 * l], sb = user[2 * l + 1];
+			if( sa < 0 || sb < 0 || owner[sa] < 0 || owner[sb] < 0 || owner[sa] == owner[sb] ) continue;
+			const int32_t same = (( sc->surfedges[sa] > 0 ) == ( sc->surfedges[sb] > 0 )) ? 0x40000000 : 0;
+			partner[sa] = owner[sb] | same;
+			partner[sb] = owner[sa] | same;
+		}
+		free( owner );
+	}
+	free( user );
+}
+
 typedef struct
 {
 	/* statics of r_rast.c that live across the edges of one face */
@@ -291,6 +352,7 @@ typedef struct
 	float   u1, v1, lzi1;
 	int32_t ceilv1;
 	float   leftenter[3], leftexit[3], rightenter[3], rightexit[3];
+	int     wrote; /* which of the four this face assigned: 1 leftexit, 2 leftenter, 4 rightexit, 8 rightenter */
 	/* output */
 	rc_edge_t *out;
 	int32_t nout, maxout;
@@ -411,8 +473,8 @@ RC_HD void rc_clip_edge( const rc_view_t *vw, rc_facestate_t *fs, const float *p
 			c[0] = a[0] + f * ( b[0] - a[0] );
 			c[1] = a[1] + f * ( b[1] - a[1] );
 			c[2] = a[2] + f * ( b[2] - a[2] );
-			if( pl == 0 ) { fs->leftclipped = 1; fs->leftexit[0] = c[0]; fs->leftexit[1] = c[1]; fs->leftexit[2] = c[2]; }
-			else if( pl == 1 ) { fs->rightclipped = 1; fs->rightexit[0] = c[0]; fs->rightexit[1] = c[1]; fs->rightexit[2] = c[2]; }
+			if( pl == 0 ) { fs->leftclipped = 1; fs->wrote |= 1; fs->leftexit[0] = c[0]; fs->leftexit[1] = c[1]; fs->leftexit[2] = c[2]; }
+			else if( pl == 1 ) { fs->rightclipped = 1; fs->wrote |= 4; fs->rightexit[0] = c[0]; fs->rightexit[1] = c[1]; fs->rightexit[2] = c[2]; }
 			b[0] = c[0]; b[1] = c[1]; b[2] = c[2];
 		}
 		else
@@ -426,12 +488,59 @@ RC_HD void rc_clip_edge( const rc_view_t *vw, rc_facestate_t *fs, const float *p
 			c[0] = a[0] + f * ( b[0] - a[0] );
 			c[1] = a[1] + f * ( b[1] - a[1] );
 			c[2] = a[2] + f * ( b[2] - a[2] );
-			if( pl == 0 ) { fs->leftclipped = 1; fs->leftenter[0] = c[0]; fs->leftenter[1] = c[1]; fs->leftenter[2] = c[2]; }
-			else if( pl == 1 ) { fs->rightclipped = 1; fs->rightenter[0] = c[0]; fs->rightenter[1] = c[1]; fs->rightenter[2] = c[2]; }
+			if( pl == 0 ) { fs->leftclipped = 1; fs->wrote |= 2; fs->leftenter[0] = c[0]; fs->leftenter[1] = c[1]; fs->leftenter[2] = c[2]; }
+			else if( pl == 1 ) { fs->rightclipped = 1; fs->wrote |= 8; fs->rightenter[0] = c[0]; fs->rightenter[1] = c[1]; fs->rightenter[2] = c[2]; }
 			a[0] = c[0]; a[1] = c[1]; a[2] = c[2];
 		}
 	}
 	rc_emit_edge( vw, fs, a, b );
+}
+
+/*
+ * R_RenderFace's edge cache (medge16_t.cachededgeoffset, r_rast.c:447-478,139-160,315-318): of the two faces that share
+ * an edge the one the walk posts first clips it and leaves one of three states behind; the second face then either
+ * skips the edge altogether (cached as "fully clipped": really clipped away, or unclipped but horizontal), reuses the
+ * emitted edge without clipping it again, or - the first face clipped it partially - processes it itself.  The state is
+ * a pure function of the first face's clip planes and direction, so the second face recomputes it here.
+ */
+enum { RC_EDGE_OWN = 0, RC_EDGE_SKIP = 1, RC_EDGE_REUSE = 2 };
+
+RC_HD int rc_first_face_edge_state( const rc_view_t *vw, const float *pv0, const float *pv1, int32_t clipflags )
+{
+	float a[3], b[3];
+	a[0] = pv0[0]; a[1] = pv0[1]; a[2] = pv0[2];
+	b[0] = pv1[0]; b[1] = pv1[1]; b[2] = pv1[2];
+	int leftclipped = 0, clipped = 0;
+	for( int pl = 0; pl < 4; pl++ )
+	{
+		if( !( clipflags & ( 1 << pl )))
+			continue;
+		float d0 = rc_dot3( a, vw->clip_normal[pl] ) - vw->clip_dist[pl];
+		float d1 = rc_dot3( b, vw->clip_normal[pl] ) - vw->clip_dist[pl];
+		if( d0 >= 0 )
+		{
+			if( d1 >= 0 )
+				continue;
+			float f = d0 / ( d0 - d1 );
+			b[0] = a[0] + f * ( b[0] - a[0] ); b[1] = a[1] + f * ( b[1] - a[1] ); b[2] = a[2] + f * ( b[2] - a[2] );
+		}
+		else
+		{
+			if( d1 < 0 )
+				return leftclipped ? RC_EDGE_OWN : RC_EDGE_SKIP; /* "if( !r_leftclipped ) cacheoffset = FULLY_CLIPPED_CACHED": even after a clip by another plane */
+			float f = d0 / ( d0 - d1 );
+			a[0] = a[0] + f * ( b[0] - a[0] ); a[1] = a[1] + f * ( b[1] - a[1] ); a[2] = a[2] + f * ( b[2] - a[2] );
+		}
+		clipped = 1;
+		if( pl == 0 ) leftclipped = 1;
+	}
+	if( clipped )
+		return RC_EDGE_OWN;
+	/* emitted unclipped: a horizontal edge is cached as fully clipped, any other is reused */
+	float u, v0, v1, lzi;
+	rc_project( vw, a, &u, &v0, &lzi );
+	rc_project( vw, b, &u, &v1, &lzi );
+	return (int32_t)ceilf( v0 ) == (int32_t)ceilf( v1 ) ? RC_EDGE_SKIP : RC_EDGE_REUSE;
 }
 
 /* D_MipLevelForScale, ref/soft/r_edge.c:697-714 */
@@ -481,67 +590,70 @@ RC_HD void rc_calc_gradients( const rc_view_t *vw, const rc_surface_t *sf, int32
 	o->bbextentt = (((int32_t)sf->lightextents[1] << 16 ) >> miplevel ) - 1;
 }
 
-/*
- * R_RenderFace (r_rast.c:384-586) for a world face + the per-surface part of D_SolidSurf /
- * D_TurbulentSurf / D_BackgroundSurf (r_edge.c:823-1053).  Edges go to fs->out (count in fs->nout,
- * which may exceed maxout: the caller treats that as overflow).  The shared-edge cache
- * (medge16_t.cachededgeoffset) is not reproduced: an edge computed twice gives bit-identical
- * values because (a-b)/(c-d) == (b-a)/(d-c) in IEEE arithmetic.
- */
-RC_HD void rc_render_face( const rc_scene_t *sc, const rc_view_t *vw, const rc_cand_t *cand, rc_facestate_t *fs, rc_surf_t *o )
+/* the edge loop of R_RenderFace for candidate ci: every surfedge clipped and emitted into fs (or skipped / reused as the
+ * edge cache dictates); reports whether a left re-entry edge / a right nearzi pass is due */
+RC_HD void rc_face_edges( const rc_scene_t *sc, const rc_view_t *vw, const rc_cand_t *cands, const uint16_t *candof, int32_t ci,
+	rc_facestate_t *fs, int *makeleftedge, int *makerightedge )
 {
+	const rc_cand_t *cand = &cands[ci];
 	const rc_surface_t *sf = &sc->surfaces[cand->surf];
 	int planes[4], nplanes = 0;
 	for( int i = 0; i < 4; i++ )
 		if( cand->clipflags & ( 1 << i ))
 			planes[nplanes++] = i;
 
-	fs->emitted = 0; fs->nearzi = 0; fs->nearzionly = 0; fs->lastvertvalid = 0;
+	fs->emitted = 0; fs->nearzi = 0; fs->nearzionly = 0; fs->lastvertvalid = 0; fs->wrote = 0;
 	fs->u1 = fs->v1 = fs->lzi1 = 0; fs->ceilv1 = 0;
-	int makeleftedge = 0, makerightedge = 0;
+	*makeleftedge = 0; *makerightedge = 0;
 
-	if( sc->sedgeverts )
-	{
-		/* both vertices of every surfedge were laid out per surfedge at upload: one load per edge, the next edge's
-		 * issued before this one is clipped */
-		const float *sv = sc->sedgeverts + (size_t)sf->firstedge * 6;
-		float cur[6], nxt[6];
-		for( int k = 0; k < 6; k++ ) cur[k] = sf->numedges > 0 ? sv[k] : 0.0f;
-		for( int32_t i = 0; i < sf->numedges; i++ )
-		{
-			if( i + 1 < sf->numedges )
-				for( int k = 0; k < 6; k++ ) nxt[k] = sv[( i + 1 ) * 6 + k];
-			fs->leftclipped = fs->rightclipped = 0;
-			rc_clip_edge( vw, fs, cur, cur + 3, planes, nplanes, 0 );
-			if( fs->leftclipped ) makeleftedge = 1;
-			if( fs->rightclipped ) makerightedge = 1;
-			fs->lastvertvalid = 1;
-			for( int k = 0; k < 6; k++ ) cur[k] = nxt[k];
-		}
-	}
-	else
+	/* both vertices of every surfedge were laid out per surfedge at upload: one load per edge, the next edge's
+	 * issued before this one is clipped */
+	const float *sv = sc->sedgeverts + (size_t)sf->firstedge * 6;
+	float cur[6], nxt[6];
+	for( int k = 0; k < 6; k++ ) cur[k] = sf->numedges > 0 ? sv[k] : 0.0f;
 	for( int32_t i = 0; i < sf->numedges; i++ )
 	{
-		int32_t lindex = sc->surfedges[sf->firstedge + i];
-		const float *v0, *v1;
-		if( lindex > 0 )
+		if( i + 1 < sf->numedges )
+			for( int k = 0; k < 6; k++ ) nxt[k] = sv[( i + 1 ) * 6 + k];
+		/* the face on the other side of this edge, when the walk posted it before this one, decided the edge's fate */
+		int state = RC_EDGE_OWN;
+		const int32_t partner = sc->sedgepartner ? sc->sedgepartner[sf->firstedge + i] : -1;
+		if( partner >= 0 )
 		{
-			v0 = sc->verts + 3 * sc->edges[2 * lindex];
-			v1 = sc->verts + 3 * sc->edges[2 * lindex + 1];
+			const int32_t pc = (int32_t)candof[partner & 0x3FFFFFFF] - 1;
+			if( pc >= 0 && pc < ci )
+				state = ( partner & 0x40000000 ) ? rc_first_face_edge_state( vw, cur, cur + 3, cands[pc].clipflags )
+					: rc_first_face_edge_state( vw, cur + 3, cur, cands[pc].clipflags );
+		}
+		fs->leftclipped = fs->rightclipped = 0;
+		if( state == RC_EDGE_OWN )
+		{
+			rc_clip_edge( vw, fs, cur, cur + 3, planes, nplanes, 0 );
+			if( fs->leftclipped ) *makeleftedge = 1;
+			if( fs->rightclipped ) *makerightedge = 1;
+			fs->lastvertvalid = 1;
 		}
 		else
 		{
-			lindex = -lindex;
-			v0 = sc->verts + 3 * sc->edges[2 * lindex + 1];
-			v1 = sc->verts + 3 * sc->edges[2 * lindex];
+			if( state == RC_EDGE_REUSE )
+			{
+				/* R_EmitCachedEdge: the edge as the first face emitted it - unclipped */
+				fs->lastvertvalid = 0;
+				rc_emit_edge( vw, fs, cur, cur + 3 );
+			}
+			fs->lastvertvalid = 0;
 		}
-		fs->leftclipped = fs->rightclipped = 0;
-		rc_clip_edge( vw, fs, v0, v1, planes, nplanes, 0 );
-		if( fs->leftclipped ) makeleftedge = 1;
-		if( fs->rightclipped ) makerightedge = 1;
-		fs->lastvertvalid = 1;
+		for( int k = 0; k < 6; k++ ) cur[k] = nxt[k];
 	}
+}
 
+/* the two passes that follow the edge loop: the left re-entry edge and the right-side nearzi */
+RC_HD void rc_face_side_edges( const rc_view_t *vw, const rc_cand_t *cand, rc_facestate_t *fs, int makeleftedge, int makerightedge )
+{
+	int planes[4], nplanes = 0;
+	for( int i = 0; i < 4; i++ )
+		if( cand->clipflags & ( 1 << i ))
+			planes[nplanes++] = i;
 	/* if there was a clip off the left edge, add that edge too (pclip->next: skip the left plane) */
 	if( makeleftedge )
 	{
@@ -557,6 +669,53 @@ RC_HD void rc_render_face( const rc_scene_t *sc, const rc_view_t *vw, const rc_c
 		while( k < nplanes && planes[k] <= 1 ) k++;
 		rc_clip_edge( vw, fs, fs->rightexit, fs->rightenter, planes, nplanes, k );
 	}
+}
+
+/*
+ * R_RenderFace (r_rast.c:384-586) for a world face + the per-surface part of D_SolidSurf /
+ * D_TurbulentSurf / D_BackgroundSurf (r_edge.c:823-1053).  Edges go to fs->out (count in fs->nout,
+ * which may exceed maxout: the caller treats that as overflow).
+ *
+ * r_leftexit / r_leftenter / r_rightexit / r_rightenter are file statics in the reference: a face whose left (right)
+ * plane clipped only one of the two edges that cross it - the other one was skipped through the edge cache - builds
+ * its re-entry edge (its right-side nearzi) from the point an EARLIER face of the frame left there.  Such a face looks
+ * the point up here by replaying the faces before it, last one first (rare: a few faces per thousand views).  A point
+ * no earlier face of the view wrote would come from the previous frame in the reference; here it is the origin.
+ */
+RC_HD void rc_render_face( const rc_scene_t *sc, const rc_view_t *vw, const rc_cand_t *cand, rc_facestate_t *fs, rc_surf_t *o,
+	const rc_cand_t *cands, const uint16_t *candof, int32_t ci )
+{
+	const rc_surface_t *sf = &sc->surfaces[cand->surf];
+	int makeleftedge = 0, makerightedge = 0;
+	for( int k = 0; k < 3; k++ ) fs->leftexit[k] = fs->leftenter[k] = fs->rightexit[k] = fs->rightenter[k] = 0.0f;
+	rc_face_edges( sc, vw, cands, candof, ci, fs, &makeleftedge, &makerightedge );
+
+	int need = ( makeleftedge ? 3 & ~fs->wrote : 0 ) | ( makerightedge ? 12 & ~fs->wrote : 0 );
+	for( int32_t k = ci - 1; k >= 0 && need; k-- )
+	{
+		/* what face k left in the four statics: its edge loop and its own side passes, nothing emitted */
+		rc_facestate_t dry;
+		int ml, mr;
+		dry.out = fs->out; dry.maxout = 0; dry.nout = 0; dry.surfnum = 0;
+		rc_face_edges( sc, vw, cands, candof, k, &dry, &ml, &mr );
+		if( !dry.wrote )
+			continue;
+		/* (its side passes read points of yet earlier faces only to clip them again: what they write is a function of
+		 * those, so a face that needs them too walks further back - handled by leaving `need` set) */
+		if(( ml && ( 3 & ~dry.wrote )) || ( mr && ( 12 & ~dry.wrote )))
+		{
+			/* face k itself ran its side passes on inherited points: its writes there cannot be told without going
+			 * further back; the main-loop writes it made are still the latest for the bits it did assign */
+		}
+		else rc_face_side_edges( vw, &cands[k], &dry, ml, mr );
+		const int take = need & dry.wrote;
+		if( take & 1 ) for( int q = 0; q < 3; q++ ) fs->leftexit[q] = dry.leftexit[q];
+		if( take & 2 ) for( int q = 0; q < 3; q++ ) fs->leftenter[q] = dry.leftenter[q];
+		if( take & 4 ) for( int q = 0; q < 3; q++ ) fs->rightexit[q] = dry.rightexit[q];
+		if( take & 8 ) for( int q = 0; q < 3; q++ ) fs->rightenter[q] = dry.rightenter[q];
+		need &= ~take;
+	}
+	rc_face_side_edges( vw, cand, fs, makeleftedge, makerightedge );
 
 	o->surf = cand->surf;
 	o->flags = sf->flags;

@@ -50,6 +50,7 @@ struct rc_work_t
 	int32_t vis_stage, vis_smem; /* k_viswalk: VW_STAGE_* flags and dynamic shared memory bytes */
 	int32_t   *walkstack; /* [nviews][stack_ints] k_viswalk scratch (rc_vis_scratch_ints) */
 	rc_cand_t *cands;
+	uint16_t  *candof;    /* [nviews][numsurfaces] candidate index + 1 of a face in its view, 0 = not listed */
 	rc_surf_t *surfs;
 	rc_edge_t *edges;
 	int32_t   *ncands, *nedges;
@@ -138,7 +139,7 @@ __global__ void __launch_bounds__( FC_THREADS ) k_faces( rc_scene_t sc, rc_work_
 	o.d_zistepu = o.d_zistepv = o.d_ziorigin = 0;
 	o.d_sdivzstepu = o.d_tdivzstepu = o.d_sdivzstepv = o.d_tdivzstepv = o.d_sdivzorigin = o.d_tdivzorigin = 0;
 	o.sadjust = o.tadjust = o.bbextents = o.bbextentt = 0;
-	rc_render_face( &sc, vw, &cand, &fs, &o );
+	rc_render_face( &sc, vw, &cand, &fs, &o, w.cands + (size_t)view * w.max_cands, w.candof + (size_t)view * ( sc.numsurfaces + 2 ), ci );
 	*out = o;
 
 	int32_t nout = fs.nout < fs.maxout ? fs.nout : fs.maxout;
@@ -497,7 +498,7 @@ struct Dev
 	int vw_grid = 0;                         /* k_viswalk: resident blocks, persistent over views */
 	unsigned long long *h_counters = nullptr; /* pinned mirror of the batch counters, copied at the end of every batch */
 	rc_view_t *d_views = nullptr;
-	void *d_work[20] = {};
+	void *d_work[24] = {};
 	bool have_batch = false;
 	void *d_flush = nullptr;
 
@@ -604,6 +605,7 @@ int ensure_batch( int nviews, int width, int height )
 #define WALLOC( field, type, count ) do { type *p = nullptr; if( dalloc( &p, (size_t)( count )) != 0 ) return -1; w.field = p; D.d_work[k++] = p; } while( 0 )
 	WALLOC( walkstack, int32_t, (size_t)D.vw_grid * RC_MAX_SLICES * w.stack_ints );
 	WALLOC( cands, rc_cand_t, (size_t)cap * w.max_cands );
+	WALLOC( candof, uint16_t, (size_t)cap * ( sc.numsurfaces + 2 ));
 	WALLOC( surfs, rc_surf_t, (size_t)cap * w.max_cands );
 	WALLOC( edges, rc_edge_t, (size_t)cap * w.max_edges );
 	WALLOC( ncands, int32_t, cap );
@@ -685,6 +687,7 @@ rc_work_t make_slice( int k, int v0, int v1 )
 	ws.views += v0;
 	ws.walkstack += (size_t)k * D.vw_grid * ws.stack_ints; /* per resident block of the slice's k_viswalk */
 	ws.cands += (size_t)v0 * ws.max_cands; ws.surfs += (size_t)v0 * ws.max_cands;
+	ws.candof += (size_t)v0 * ( sc.numsurfaces + 2 );
 	ws.edges += (size_t)v0 * ws.max_edges;
 	ws.ncands += v0; ws.nedges += v0;
 	ws.bandnloc += (size_t)v0 * ws.nbands;
@@ -949,24 +952,15 @@ int rc_dev_upload_scene( const rc_scene_t *sc, size_t cache_texels )
 		if( upload( &surfback, sb.data(), sb.size()) != 0 ) return -1;
 	}
 	float *sedgeverts = (float *)D.d_scene[14];
+	int32_t *sedgepartner = (int32_t *)D.d_scene[15];
 	{
 		std::vector<float> sv((size_t)( sc->numsurfedges > 0 ? sc->numsurfedges : 1 ) * 6, 0.0f );
-		for( int32_t i = 0; i < sc->numsurfedges; i++ )
-		{
-			int32_t l = sc->surfedges[i];
-			const int a = l > 0 ? 0 : 1;
-			if( l < 0 ) l = -l;
-			if( l >= sc->numedges ) continue;
-			const int32_t i0 = sc->edges[2 * l + a], i1 = sc->edges[2 * l + ( a ^ 1 )];
-			if( i0 >= sc->numverts || i1 >= sc->numverts ) continue;
-			for( int k = 0; k < 3; k++ )
-			{
-				sv[(size_t)i * 6 + k] = sc->verts[3 * i0 + k];
-				sv[(size_t)i * 6 + 3 + k] = sc->verts[3 * i1 + k];
-			}
-		}
+		std::vector<int32_t> sp((size_t)( sc->numsurfedges > 0 ? sc->numsurfedges : 1 ), -1 );
+		rc_build_sedge_tables( sc, sv.data(), sp.data());
 		if( upload( &sedgeverts, sv.data(), sv.size()) != 0 ) return -1;
+		if( upload( &sedgepartner, sp.data(), sp.size()) != 0 ) return -1;
 	}
+	D.d_scene[15] = sedgepartner; d.sedgepartner = sedgepartner;
 	D.d_scene[11] = pvsdense; D.d_scene[12] = surfnode; D.d_scene[13] = surfback; D.d_scene[14] = sedgeverts;
 	d.pvsdense = pvsdense; d.surfnode = surfnode; d.surfback = surfback; d.sedgeverts = sedgeverts;
 	D.d_scene[0] = planes; D.d_scene[1] = nodes; D.d_scene[2] = leafs; D.d_scene[3] = surfaces; D.d_scene[4] = marks;

@@ -470,11 +470,15 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 	}
 	const int32_t total = carry;
 	rc_cand_t *cands = w.cands + (size_t)view * w.max_cands;
+	uint16_t *candof = w.candof + (size_t)view * ( sc.numsurfaces + 2 );
 	for( int32_t s = t; s < sc.numsurfaces; s += VW_THREADS )
 	{
 		const int32_t wi = s >> 5, b = s & 31;
 		if( !(( surfmark[wi] >> b ) & 1 ))
+		{
+			candof[s] = 0;
 			continue;
+		}
 		const int32_t n = sn16 ? (int32_t)sn16[s] : sc.surfnode[s], pos = nodepos[n];
 		/* rank among the node's candidates: surviving marks in [firstsurface, s) */
 		const int32_t f = sc.nodes[n].firstsurface;
@@ -487,6 +491,7 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 			rank += __popc( mk );
 		}
 		const int32_t o = seq[pos] + rank;
+		candof[s] = o < w.max_cands ? (uint16_t)( o + 1 ) : (uint16_t)0;
 		if( o < w.max_cands )
 		{
 			cands[o].surf = s;

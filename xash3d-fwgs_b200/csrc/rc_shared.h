@@ -111,6 +111,9 @@ typedef struct
 	const uint32_t     *surfback;  /* [numsurfaces bits] SURF_PLANEBACK */
 	const float        *sedgeverts;/* [numsurfedges][6] both vertices of every surfedge in its winding direction: one load
 	                                * instead of the surfedges -> edges -> verts chain of three dependent ones */
+	const int32_t      *sedgepartner;/* [numsurfedges] the other face that lists the same medge (R_RenderFace's edge cache,
+	                                * ref/soft/r_rast.c:447-478, couples the two), bit 30 set: it walks the edge in the same
+	                                * direction; -1: none */
 } rc_scene_t;
 
 /* an active dynamic light of the batch (dlight_t, common/q_client.h:57, after R_PushDlights' die / radius test) */
