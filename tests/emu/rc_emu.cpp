@@ -170,12 +170,27 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 		std::vector<uint16_t> candof( sc->numsurfaces + 2, 0 );
 		for( int ci = 0; ci < ncands; ci++ ) candof[cands[ci].surf] = (uint16_t)( ci + 1 );
 		std::vector<rc_edge_t> edges;
+		std::vector<rc_facerec_t> recs( ncands + 1 );
 		for( int ci = 0; ci < ncands; ci++ )
 		{
+			/* as the kernels do it: k_faces begins every face and leaves its record; a face that has to inherit a clip
+			 * point is finished afterwards (k_faces_fix) - the record of such a face keeps what its edge loop wrote */
 			rc_edge_t local[256];
 			rc_facestate_t fs; memset( &fs, 0, sizeof( fs ));
 			fs.out = local; fs.maxout = 256; fs.surfnum = ci + 1;
-			rc_render_face( sc, vw, &cands[ci], &fs, &surfs[ci], cands.data(), candof.data(), ci );
+			int ml, mr;
+			const int need = rc_face_begin( sc, vw, cands.data(), candof.data(), ci, &fs, &ml, &mr );
+			if( need )
+			{
+				rc_face_store( &fs, ml, mr, 1, &recs[ci] );
+				rc_face_inherit( recs.data(), ci, need, &fs );
+				rc_face_finish( sc, vw, &cands[ci], &fs, ml, mr, &surfs[ci] );
+			}
+			else
+			{
+				rc_face_finish( sc, vw, &cands[ci], &fs, ml, mr, &surfs[ci] );
+				rc_face_store( &fs, ml, mr, 0, &recs[ci] );
+			}
 			for( int k = 0; k < fs.nout && k < 256; k++ ) edges.push_back( local[k] );
 			if( surfs[ci].emitted )
 			{

@@ -673,48 +673,71 @@ RC_HD void rc_face_side_edges( const rc_view_t *vw, const rc_cand_t *cand, rc_fa
 
 /*
  * R_RenderFace (r_rast.c:384-586) for a world face + the per-surface part of D_SolidSurf /
- * D_TurbulentSurf / D_BackgroundSurf (r_edge.c:823-1053).  Edges go to fs->out (count in fs->nout,
- * which may exceed maxout: the caller treats that as overflow).
- *
- * r_leftexit / r_leftenter / r_rightexit / r_rightenter are file statics in the reference: a face whose left (right)
- * plane clipped only one of the two edges that cross it - the other one was skipped through the edge cache - builds
- * its re-entry edge (its right-side nearzi) from the point an EARLIER face of the frame left there.  Such a face looks
- * the point up here by replaying the faces before it, last one first (rare: a few faces per thousand views).  A point
- * no earlier face of the view wrote would come from the previous frame in the reference; here it is the origin.
+ * D_TurbulentSurf / D_BackgroundSurf (r_edge.c:823-1053), in three steps:
+ *   rc_face_begin   the edge loop (rc_face_edges); leaves a record of what the face did to r_leftexit / r_leftenter /
+ *                   r_rightexit / r_rightenter, file statics of r_rast.c
+ *   rc_face_inherit for the rare face whose left (right) plane clipped only one of the two edges that cross it - the
+ *                   other was skipped through the edge cache - the missing point is whatever an EARLIER face of the frame
+ *                   left in the static: the records of the faces before it are searched, last one first.  A point no
+ *                   earlier face of the view wrote would come from the previous frame in the reference; here it is the origin.
+ *   rc_face_finish  left re-entry edge, right-side nearzi, surf_t fields, mip level, gradients.
+ * Edges go to fs->out (count in fs->nout, which may exceed maxout: the caller treats that as overflow).
  */
-RC_HD void rc_render_face( const rc_scene_t *sc, const rc_view_t *vw, const rc_cand_t *cand, rc_facestate_t *fs, rc_surf_t *o,
-	const rc_cand_t *cands, const uint16_t *candof, int32_t ci )
+typedef struct
 {
-	const rc_surface_t *sf = &sc->surfaces[cand->surf];
-	int makeleftedge = 0, makerightedge = 0;
-	for( int k = 0; k < 3; k++ ) fs->leftexit[k] = fs->leftenter[k] = fs->rightexit[k] = fs->rightenter[k] = 0.0f;
-	rc_face_edges( sc, vw, cands, candof, ci, fs, &makeleftedge, &makerightedge );
+	float   pts[4][3];  /* leftexit, leftenter, rightexit, rightenter as the face left them */
+	int32_t wrote;      /* bit i: pts[i] assigned by this face */
+	int32_t state;      /* 1 make left edge, 2 make right edge, 4 emitted, 8 waits for rc_face_inherit */
+	float   nearzi;
+	int32_t nout;
+} rc_facerec_t; /* 64 B */
 
-	int need = ( makeleftedge ? 3 & ~fs->wrote : 0 ) | ( makerightedge ? 12 & ~fs->wrote : 0 );
+RC_HD int rc_face_need( int makeleftedge, int makerightedge, int wrote )
+{
+	return ( makeleftedge ? 3 & ~wrote : 0 ) | ( makerightedge ? 12 & ~wrote : 0 );
+}
+
+RC_HD void rc_face_store( const rc_facestate_t *fs, int makeleftedge, int makerightedge, int waits, rc_facerec_t *r )
+{
+	for( int q = 0; q < 3; q++ )
+	{
+		r->pts[0][q] = fs->leftexit[q]; r->pts[1][q] = fs->leftenter[q];
+		r->pts[2][q] = fs->rightexit[q]; r->pts[3][q] = fs->rightenter[q];
+	}
+	r->wrote = fs->wrote;
+	r->state = ( makeleftedge ? 1 : 0 ) | ( makerightedge ? 2 : 0 ) | ( fs->emitted ? 4 : 0 ) | ( waits ? 8 : 0 );
+	r->nearzi = fs->nearzi;
+	r->nout = fs->nout;
+}
+
+RC_HD int rc_face_begin( const rc_scene_t *sc, const rc_view_t *vw, const rc_cand_t *cands, const uint16_t *candof, int32_t ci,
+	rc_facestate_t *fs, int *makeleftedge, int *makerightedge )
+{
+	for( int k = 0; k < 3; k++ ) fs->leftexit[k] = fs->leftenter[k] = fs->rightexit[k] = fs->rightenter[k] = 0.0f;
+	rc_face_edges( sc, vw, cands, candof, ci, fs, makeleftedge, makerightedge );
+	return rc_face_need( *makeleftedge, *makerightedge, fs->wrote );
+}
+
+/* recs: the records of the view's candidates (those before ci are read) */
+RC_HD void rc_face_inherit( const rc_facerec_t *recs, int32_t ci, int need, rc_facestate_t *fs )
+{
 	for( int32_t k = ci - 1; k >= 0 && need; k-- )
 	{
-		/* what face k left in the four statics: its edge loop and its own side passes, nothing emitted */
-		rc_facestate_t dry;
-		int ml, mr;
-		dry.out = fs->out; dry.maxout = 0; dry.nout = 0; dry.surfnum = 0;
-		rc_face_edges( sc, vw, cands, candof, k, &dry, &ml, &mr );
-		if( !dry.wrote )
+		const int take = need & recs[k].wrote;
+		if( !take )
 			continue;
-		/* (its side passes read points of yet earlier faces only to clip them again: what they write is a function of
-		 * those, so a face that needs them too walks further back - handled by leaving `need` set) */
-		if(( ml && ( 3 & ~dry.wrote )) || ( mr && ( 12 & ~dry.wrote )))
-		{
-			/* face k itself ran its side passes on inherited points: its writes there cannot be told without going
-			 * further back; the main-loop writes it made are still the latest for the bits it did assign */
-		}
-		else rc_face_side_edges( vw, &cands[k], &dry, ml, mr );
-		const int take = need & dry.wrote;
-		if( take & 1 ) for( int q = 0; q < 3; q++ ) fs->leftexit[q] = dry.leftexit[q];
-		if( take & 2 ) for( int q = 0; q < 3; q++ ) fs->leftenter[q] = dry.leftenter[q];
-		if( take & 4 ) for( int q = 0; q < 3; q++ ) fs->rightexit[q] = dry.rightexit[q];
-		if( take & 8 ) for( int q = 0; q < 3; q++ ) fs->rightenter[q] = dry.rightenter[q];
+		if( take & 1 ) for( int q = 0; q < 3; q++ ) fs->leftexit[q] = recs[k].pts[0][q];
+		if( take & 2 ) for( int q = 0; q < 3; q++ ) fs->leftenter[q] = recs[k].pts[1][q];
+		if( take & 4 ) for( int q = 0; q < 3; q++ ) fs->rightexit[q] = recs[k].pts[2][q];
+		if( take & 8 ) for( int q = 0; q < 3; q++ ) fs->rightenter[q] = recs[k].pts[3][q];
 		need &= ~take;
 	}
+}
+
+RC_HD void rc_face_finish( const rc_scene_t *sc, const rc_view_t *vw, const rc_cand_t *cand, rc_facestate_t *fs,
+	int makeleftedge, int makerightedge, rc_surf_t *o )
+{
+	const rc_surface_t *sf = &sc->surfaces[cand->surf];
 	rc_face_side_edges( vw, cand, fs, makeleftedge, makerightedge );
 
 	o->surf = cand->surf;

@@ -19,6 +19,7 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <vector>
@@ -51,6 +52,10 @@ struct rc_work_t
 	int32_t   *walkstack; /* [nviews][stack_ints] k_viswalk scratch (rc_vis_scratch_ints) */
 	rc_cand_t *cands;
 	uint16_t  *candof;    /* [nviews][numsurfaces] candidate index + 1 of a face in its view, 0 = not listed */
+	rc_facerec_t *facerecs; /* [nviews][max_cands] what every face left in r_rast.c's clip-point statics */
+	uint8_t   *facewrote; /* [nviews][max_cands] rc_facerec_t.wrote, packed for the backward search */
+	int32_t   *fix_list, *fix_count; /* faces that wait for an earlier face's clip point: {view, candidate, first edge slot} */
+	int32_t    fix_cap;
 	rc_surf_t *surfs;
 	rc_edge_t *edges;
 	int32_t   *ncands, *nedges;
@@ -60,6 +65,7 @@ struct rc_work_t
 	int32_t   *cache_nlist, *cache_cursor;
 	int32_t   *line_cursor; /* k_lines work cursors: heavy list, all lines */
 	int32_t   *heavy_list, *heavy_count; /* [nviews * height] lines with more than LN_HEAVY events (k_events), their number */
+	int32_t   *wide_list, *wide_count;   /* [nviews * height] lines for k_lines_wide (RC_LINE_WIDE), their number */
 	const int32_t *styles;/* [256] g_lightstylevalue */
 	const rc_dlight_t *dlights; /* active dynamic lights of the batch */
 	const uint32_t *dlightbits; /* [numsurfaces] msurface_t.dlightbits (k_dlight_mark) */
@@ -104,6 +110,42 @@ __device__ __forceinline__ int32_t rc_warp_incl_scan( int32_t x, int lane )
 
 #define FC_THREADS 64
 
+/* the end of a face: side passes, surf_t record, unused edge reservations, the cache block it samples, counters */
+__device__ __forceinline__ void rc_face_commit( const rc_scene_t &sc, const rc_work_t &w, int view, int ci, const rc_cand_t *cand,
+	rc_facestate_t *fs, int ml, int mr, rc_surf_t *out )
+{
+	(void)ci;
+	rc_surf_t o;
+	o.miplevel = 0; o.cache_ofs = -1; o.cachewidth = 0;
+	o.d_zistepu = o.d_zistepv = o.d_ziorigin = 0;
+	o.d_sdivzstepu = o.d_tdivzstepu = o.d_sdivzstepv = o.d_tdivzstepv = o.d_sdivzorigin = o.d_tdivzorigin = 0;
+	o.sadjust = o.tadjust = o.bbextents = o.bbextentt = 0;
+	rc_face_finish( &sc, &w.views[view], cand, fs, ml, mr, &o );
+	*out = o;
+
+	int32_t nout = fs->nout < fs->maxout ? fs->nout : fs->maxout;
+	/* unused reservations become edges that are never active */
+	for( int32_t k = nout; k < fs->maxout; k++ )
+	{
+		fs->out[k].u = 0; fs->out[k].u_step = 0; fs->out[k].vv = 1u; fs->out[k].surfs = 0;
+	}
+	if( o.emitted && !( o.flags & ( RC_SURF_DRAWSKY | RC_SURF_DRAWTURB )) && o.cache_ofs >= 0 )
+	{
+		int32_t slot = cand->surf * 4 + o.miplevel;
+		atomicOr( &w.cache_need[slot >> 5], 1u << ( slot & 31 ));
+	}
+	/* batch counters: one atomic per warp (tens of thousands of threads adding to one address serialise in L2) */
+	{
+		const unsigned m = __activemask();
+		const unsigned ns = __reduce_add_sync( m, o.emitted ? 1u : 0u ), ne = __reduce_add_sync( m, (unsigned)nout );
+		if(( threadIdx.x & 31 ) == __ffs( (int)m ) - 1 )
+		{
+			if( ns ) atomicAdd( &w.counters[RC_CTR_SURFS], (unsigned long long)ns );
+			if( ne ) atomicAdd( &w.counters[RC_CTR_EDGES], (unsigned long long)ne );
+		}
+	}
+}
+
 __global__ void __launch_bounds__( FC_THREADS ) k_faces( rc_scene_t sc, rc_work_t w )
 {
 	const int view = blockIdx.x;
@@ -134,35 +176,83 @@ __global__ void __launch_bounds__( FC_THREADS ) k_faces( rc_scene_t sc, rc_work_
 		atomicAdd( &w.counters[RC_CTR_OVERFLOW_EDGES], 1ull );
 	}
 
-	rc_surf_t o;
-	o.miplevel = 0; o.cache_ofs = -1; o.cachewidth = 0;
-	o.d_zistepu = o.d_zistepv = o.d_ziorigin = 0;
-	o.d_sdivzstepu = o.d_tdivzstepu = o.d_sdivzstepv = o.d_tdivzstepv = o.d_sdivzorigin = o.d_tdivzorigin = 0;
-	o.sadjust = o.tadjust = o.bbextents = o.bbextentt = 0;
-	rc_render_face( &sc, vw, &cand, &fs, &o, w.cands + (size_t)view * w.max_cands, w.candof + (size_t)view * ( sc.numsurfaces + 2 ), ci );
-	*out = o;
-
-	int32_t nout = fs.nout < fs.maxout ? fs.nout : fs.maxout;
-	/* unused reservations become edges that are never active */
-	for( int32_t k = nout; k < fs.maxout; k++ )
+	const rc_cand_t *vcands = w.cands + (size_t)view * w.max_cands;
+	rc_facerec_t *recs = w.facerecs + (size_t)view * w.max_cands;
+	int ml, mr;
+	const int need = rc_face_begin( &sc, vw, vcands, w.candof + (size_t)view * ( sc.numsurfaces + 2 ), ci, &fs, &ml, &mr );
+	if( need )
 	{
-		fs.out[k].u = 0; fs.out[k].u_step = 0; fs.out[k].vv = 1u; fs.out[k].surfs = 0;
-	}
-
-	if( o.emitted && !( o.flags & ( RC_SURF_DRAWSKY | RC_SURF_DRAWTURB )) && o.cache_ofs >= 0 )
-	{
-		int32_t slot = cand.surf * 4 + o.miplevel;
-		atomicOr( &w.cache_need[slot >> 5], 1u << ( slot & 31 ));
-	}
-	/* batch counters: one atomic per warp (tens of thousands of threads adding to one address serialise in L2) */
-	{
-		const unsigned m = __activemask();
-		const unsigned ns = __reduce_add_sync( m, o.emitted ? 1u : 0u ), ne = __reduce_add_sync( m, (unsigned)nout );
-		if(( threadIdx.x & 31 ) == __ffs( (int)m ) - 1 )
+		/* one of the clip points this face builds its left re-entry edge / right nearzi from is an earlier face's: the
+		 * records of the faces before it are complete only when this kernel is: k_faces_fix finishes the face */
+		const int32_t slot = atomicAdd( w.fix_count, 1 );
+		if( slot < w.fix_cap )
 		{
-			if( ns ) atomicAdd( &w.counters[RC_CTR_SURFS], (unsigned long long)ns );
-			if( ne ) atomicAdd( &w.counters[RC_CTR_EDGES], (unsigned long long)ne );
+			rc_face_store( &fs, ml, mr, 1, &recs[ci] );
+			w.facewrote[(size_t)view * w.max_cands + ci] = (uint8_t)fs.wrote;
+			w.fix_list[3 * slot] = view; w.fix_list[3 * slot + 1] = ci; w.fix_list[3 * slot + 2] = first;
+			return;
 		}
+		atomicAdd( &w.counters[RC_CTR_OVERFLOW_FIX], 1ull ); /* finished here with the point at the origin; reported */
+	}
+	rc_face_commit( sc, w, view, ci, &cand, &fs, ml, mr, out );
+	rc_face_store( &fs, ml, mr, 0, &recs[ci] );
+	w.facewrote[(size_t)view * w.max_cands + ci] = (uint8_t)fs.wrote;
+}
+
+/* the faces k_faces left waiting for an earlier face's clip point (a few per view): a warp per face - the lanes look at
+ * the 32 faces before it at a time (one byte each: which of the four points that face wrote), the nearest writer of
+ * every missing point is picked with a ballot; lane 0 then finishes the face */
+__global__ void __launch_bounds__( FC_THREADS ) k_faces_fix( rc_scene_t sc, rc_work_t w )
+{
+	int32_t n = *w.fix_count;
+	if( n > w.fix_cap ) n = w.fix_cap;
+	const int lane = threadIdx.x & 31;
+	const int32_t nwarps = gridDim.x * ( FC_THREADS / 32 );
+	for( int32_t i = blockIdx.x * ( FC_THREADS / 32 ) + ( threadIdx.x >> 5 ); i < n; i += nwarps )
+	{
+		const int32_t view = w.fix_list[3 * i], ci = w.fix_list[3 * i + 1], first = w.fix_list[3 * i + 2];
+		const rc_facerec_t *recs = w.facerecs + (size_t)view * w.max_cands;
+		const uint8_t *wrote = w.facewrote + (size_t)view * w.max_cands;
+		const rc_facerec_t me = recs[ci];
+		const int ml = me.state & 1, mr = ( me.state >> 1 ) & 1;
+		int need = rc_face_need( ml, mr, me.wrote );
+		float pts[4][3];
+		for( int b = 0; b < 4; b++ ) for( int q = 0; q < 3; q++ ) pts[b][q] = me.pts[b][q];
+		for( int32_t base = ci - 1; base >= 0 && need; base -= 32 )
+		{
+			const int32_t k = base - lane;
+			const int take = k >= 0 ? ( (int)wrote[k] & need ) : 0;
+#pragma unroll
+			for( int b = 0; b < 4; b++ )
+			{
+				const uint32_t m = __ballot_sync( 0xFFFFFFFFu, take & ( 1 << b ));
+				if( m )
+				{
+					const rc_facerec_t *src = &recs[base - ( __ffs( (int)m ) - 1 )]; /* the lowest lane is the nearest face */
+					for( int q = 0; q < 3; q++ ) pts[b][q] = src->pts[b][q];
+					need &= ~( 1 << b );
+				}
+			}
+		}
+		if( lane == 0 )
+		{
+			const rc_cand_t cand = w.cands[(size_t)view * w.max_cands + ci];
+			const rc_surface_t *sf = &sc.surfaces[cand.surf];
+			rc_facestate_t fs;
+			fs.out = w.edges + (size_t)view * w.max_edges + first;
+			fs.maxout = first + sf->numedges + 1 > w.max_edges ? 0 : sf->numedges + 1;
+			fs.nout = me.nout;
+			fs.surfnum = (uint32_t)ci + 1;
+			fs.emitted = ( me.state & 4 ) ? 1 : 0; fs.nearzi = me.nearzi; fs.nearzionly = 0; fs.lastvertvalid = 0; fs.wrote = me.wrote;
+			fs.u1 = fs.v1 = fs.lzi1 = 0; fs.ceilv1 = 0; fs.leftclipped = fs.rightclipped = 0;
+			for( int q = 0; q < 3; q++ )
+			{
+				fs.leftexit[q] = pts[0][q]; fs.leftenter[q] = pts[1][q]; fs.rightexit[q] = pts[2][q]; fs.rightenter[q] = pts[3][q];
+			}
+			rc_face_commit( sc, w, view, ci, &cand, &fs, ml, mr, &w.surfs[(size_t)view * w.max_cands + ci] );
+			atomicAdd( &w.counters[RC_CTR_FIXED_FACES], 1ull );
+		}
+		__syncwarp();
 	}
 }
 
@@ -468,6 +558,7 @@ struct Dev
 	bool cache_aside = true;                               /* false: on the slice's own stream (the bench times the kernels alone) */
 	cudaEvent_t ev[8] = {};
 	uint64_t launches = 0, h2d_bytes = 0;
+	bool sync_each = false; /* RC_SYNC_EACH in the environment: synchronise and check after every kernel (names the one that faults) */
 
 	rc_scene_t sc{};            /* device pointers */
 	std::vector<rc_surface_t> h_surfaces;
@@ -522,6 +613,7 @@ bool ck( cudaError_t e, const char *what )
 	return false;
 }
 #define CK( call ) do { if( !ck(( call ), #call )) return -1; } while( 0 )
+#define KCHECK( name, st ) do { if( D.sync_each ) { cudaError_t e_ = cudaStreamSynchronize( st ); if( e_ == cudaSuccess ) e_ = cudaGetLastError(); if( e_ != cudaSuccess ) { snprintf( D.err, sizeof( D.err ), "kernel %s: %s", name, cudaGetErrorString( e_ )); return -1; } } } while( 0 )
 
 template <typename T> int upload( T **dst, const T *src, size_t n )
 {
@@ -606,6 +698,10 @@ int ensure_batch( int nviews, int width, int height )
 	WALLOC( walkstack, int32_t, (size_t)D.vw_grid * RC_MAX_SLICES * w.stack_ints );
 	WALLOC( cands, rc_cand_t, (size_t)cap * w.max_cands );
 	WALLOC( candof, uint16_t, (size_t)cap * ( sc.numsurfaces + 2 ));
+	WALLOC( facerecs, rc_facerec_t, (size_t)cap * w.max_cands );
+	WALLOC( facewrote, uint8_t, (size_t)cap * w.max_cands );
+	w.fix_cap = cap * 16 + 1024;
+	WALLOC( fix_list, int32_t, (size_t)3 * w.fix_cap * RC_MAX_SLICES );
 	WALLOC( surfs, rc_surf_t, (size_t)cap * w.max_cands );
 	WALLOC( edges, rc_edge_t, (size_t)cap * w.max_edges );
 	WALLOC( ncands, int32_t, cap );
@@ -622,6 +718,7 @@ int ensure_batch( int nviews, int width, int height )
 	WALLOC( events, unsigned long long, (size_t)cap * w.view_events );
 	WALLOC( lineinfo, rc_lineinfo_t, (size_t)cap * height );
 	WALLOC( heavy_list, int32_t, (size_t)cap * height );
+	WALLOC( wide_list, int32_t, (size_t)cap * height );
 	WALLOC( color, uint16_t, (size_t)cap * width * height );
 	WALLOC( zbuf, int16_t, (size_t)cap * width * height );
 #undef WALLOC
@@ -688,6 +785,9 @@ rc_work_t make_slice( int k, int v0, int v1 )
 	ws.walkstack += (size_t)k * D.vw_grid * ws.stack_ints; /* per resident block of the slice's k_viswalk */
 	ws.cands += (size_t)v0 * ws.max_cands; ws.surfs += (size_t)v0 * ws.max_cands;
 	ws.candof += (size_t)v0 * ( sc.numsurfaces + 2 );
+	ws.facerecs += (size_t)v0 * ws.max_cands;
+	ws.facewrote += (size_t)v0 * ws.max_cands;
+	ws.fix_list += (size_t)3 * ws.fix_cap * k; ws.fix_count = D.d_nlist + 8 * k + 7;
 	ws.edges += (size_t)v0 * ws.max_edges;
 	ws.ncands += v0; ws.nedges += v0;
 	ws.bandnloc += (size_t)v0 * ws.nbands;
@@ -699,8 +799,9 @@ rc_work_t make_slice( int k, int v0, int v1 )
 	ws.cache_need = D.d_need + (size_t)k * ( nslots / 32 + 2 );
 	ws.cache_keys = D.d_keys;
 	ws.cache_list = D.d_list + (size_t)k * nslots;
-	ws.cache_nlist = D.d_nlist + 8 * k; ws.cache_cursor = ws.cache_nlist + 1; ws.line_cursor = ws.cache_nlist + 2; ws.heavy_count = ws.cache_nlist + 4;
+	ws.cache_nlist = D.d_nlist + 8 * k; ws.cache_cursor = ws.cache_nlist + 1; ws.line_cursor = ws.cache_nlist + 2; ws.heavy_count = ws.cache_nlist + 5; ws.wide_count = ws.cache_nlist + 6;
 	ws.heavy_list += (size_t)v0 * ws.height;
+	ws.wide_list += (size_t)v0 * ws.height;
 	ws.styles = D.d_styles; ws.counters = D.d_counters;
 	ws.dlights = D.d_dlights; ws.dlightbits = D.d_dlightbits; ws.ndlights = D.ndlights;
 	return ws;
@@ -715,12 +816,16 @@ int launch_slice( const rc_work_t &ws, int k, cudaStream_t st, cudaEvent_t *evs,
 	if( evs ) CK( cudaEventRecord( evs[0], st ));
 	k_viswalk<VW_NTHREADS><<<ws.nviews < D.vw_grid ? ws.nviews : D.vw_grid, VW_NTHREADS, (size_t)ws.vis_smem, st>>>( sc, ws );
 	D.launches++;
+	KCHECK( "k_viswalk", st );
 	if( evs ) CK( cudaEventRecord( evs[1], st ));
 	{
 		/* x = view: the blocks that have candidates (the first chunks of every view) are issued first, ahead of the
 		 * thousands of empty ones (max_cands is the face count of the map) */
 		dim3 g( ws.nviews, ( ws.max_cands + FC_THREADS - 1 ) / FC_THREADS );
 		k_faces<<<g, FC_THREADS, 0, st>>>( sc, ws ); D.launches++;
+		KCHECK( "k_faces", st );
+		k_faces_fix<<<D.num_sms * 2, FC_THREADS, 0, st>>>( sc, ws ); D.launches++;
+		KCHECK( "k_faces_fix", st );
 	}
 	if( evs ) CK( cudaEventRecord( evs[2], st ));
 	{
@@ -731,6 +836,7 @@ int launch_slice( const rc_work_t &ws, int k, cudaStream_t st, cudaEvent_t *evs,
 		int nslots = sc.numsurfaces * 4;
 		k_cache_list<<<( nslots + 255 ) / 256, 256, 0, aux>>>( sc, ws ); D.launches++;
 		k_cache_build<<<148 * 4, CACHE_THREADS, 0, aux>>>( sc, ws ); D.launches++;
+		KCHECK( "k_cache_list/build", aux );
 		CK( cudaEventRecord( D.ev_cache[k][1], aux ));
 	}
 	if( evs ) CK( cudaEventRecord( evs[3], st ));
@@ -738,8 +844,13 @@ int launch_slice( const rc_work_t &ws, int k, cudaStream_t st, cudaEvent_t *evs,
 	{
 		dim3 g( ws.nviews, ws.nbands ); /* x = view: blocks are issued band by band, see k_events */
 		k_events<<<g, EV_THREADS, rc_events_smem( ws.ev_ecap, ws.scanbits_words ), st>>>( ws ); D.launches++;
+		KCHECK( "k_events", st );
 		const int lblocks = ( nlines + LN_WARPS - 1 ) / LN_WARPS;
 		k_lines<<<lblocks < LN_GRID ? lblocks : LN_GRID, LN_WARPS * 32, 0, st>>>( ws ); D.launches++;
+		KCHECK( "k_lines", st );
+		/* the few lines with more events / band surfaces than k_lines takes (none on small maps: the blocks find an empty list) */
+		k_lines_wide<<<WD_GRID, WD_THREADS, 0, st>>>( ws ); D.launches++;
+		KCHECK( "k_lines_wide", st );
 	}
 	if( evs ) CK( cudaEventRecord( evs[4], st ));
 	if( D.cache_aside ) CK( cudaStreamWaitEvent( st, D.ev_cache[k][1], 0 ));
@@ -749,6 +860,7 @@ int launch_slice( const rc_work_t &ws, int k, cudaStream_t st, cudaEvent_t *evs,
 		const int dblocks = ( nlines / lpw + DR_WARPS - 1 ) / DR_WARPS;
 		k_draw<<<dblocks < DR_GRID ? dblocks : DR_GRID, DR_WARPS * 32, rc_draw_smem( ws.width, lpw ), st>>>( sc, ws, 0, nlines, lpw );
 		D.launches++;
+		KCHECK( "k_draw", st );
 	}
 	if( evs ) CK( cudaEventRecord( evs[5], st ));
 	return 0;
@@ -817,6 +929,7 @@ int rc_dev_init( int device )
 	CK( cudaGetDeviceProperties( &prop, device ));
 	snprintf( D.name, sizeof( D.name ), "%s (sm_%d%d, %d SMs)", prop.name, prop.major, prop.minor, prop.multiProcessorCount );
 	D.device = device; D.num_sms = prop.multiProcessorCount;
+	D.sync_each = getenv( "RC_SYNC_EACH" ) != nullptr;
 	CK( cudaHostAlloc( (void **)&D.h_counters, sizeof( unsigned long long ) * RC_CTR_COUNT, cudaHostAllocDefault ));
 	memset( D.h_counters, 0, sizeof( unsigned long long ) * RC_CTR_COUNT );
 	CK( cudaStreamCreateWithFlags( &D.stream, cudaStreamNonBlocking ));

@@ -27,7 +27,12 @@
 #define LN_WARPS    4
 #define LN_HEAVY    128  /* events: lines above are listed by k_events and go first (measured: 32: 166 us, 64: 159, 128: 153, 192: 159) */
 #define LN_CHUNK    1    /* scanlines a warp takes from the shared cursor at a time (measured on the C2 batch: 1: 170 us, 2: 172, 4: 183, 8: 184) */
-#define SP_SORTCAP  512  /* events per line the shared-memory sorter takes; longer lines fall back to a serial sort */
+#define SP_SORTCAP  512  /* events per line k_lines sorts in shared memory; longer lines go to k_lines_wide */
+#define WD_SORTCAP  4096 /* events per line k_lines_wide sorts in shared memory (a block per line); beyond: serial */
+#define WD_THREADS  128
+#define WD_GRID     ( 148 * 4 )
+#define RC_LINE_WIDE 0x20000000 /* set in nsp by k_events: more events than k_lines sorts or more band-local surfaces than its
+                                 * register bit sets hold - the line is k_lines_wide's */
 #define SP_BITWORDS 64   /* shared-memory bit-set words per line (views listing <= 2015 faces), else global scratch */
 #define SP_EXCCAP   8
 #define SP_OEPASSES 6  /* odd-even transposition passes tried on a nearly sorted line before the bitonic network */
@@ -260,7 +265,12 @@ __global__ void __launch_bounds__( EV_THREADS ) k_events( rc_work_t w )
 		{
 			li.ofs = band * w.blk_events + off; /* index inside the view's arena */
 			li.nsp = n;                         /* events for now; k_lines replaces it with the span count */
-			if( n > LN_HEAVY ) w.heavy_list[atomicAdd( w.heavy_count, 1 )] = view * w.height + y;
+			if( n > SP_SORTCAP || (( nlocal + 32 ) >> 5 ) > 16 )
+			{
+				li.nsp |= RC_LINE_WIDE;
+				w.wide_list[atomicAdd( w.wide_count, 1 )] = view * w.height + y;
+			}
+			else if( n > LN_HEAVY ) w.heavy_list[atomicAdd( w.heavy_count, 1 )] = view * w.height + y;
 		}
 		else if( valid )
 			atomicAdd( &w.counters[RC_CTR_OVERFLOW_EVENTS], 1ull );
@@ -476,8 +486,8 @@ __global__ void __launch_bounds__( LN_WARPS * 32, 8 ) k_lines( rc_work_t w )
 		if( li.ofs < 0 )
 			continue;
 		const int32_t n = li.nsp;
-		if(( n & RC_LINE_DONE ) || ( !heavy && n > LN_HEAVY ))
-			continue; /* done in the first sweep */
+		if(( n & ( RC_LINE_DONE | RC_LINE_WIDE )) || ( !heavy && n > LN_HEAVY ))
+			continue; /* done in the first sweep, or k_lines_wide's */
 		const rc_view_t *vw = &w.views[view];
 		const int32_t x0 = vw->vrect[0], vw_w = vw->vrect[2];
 #ifdef RC_SPANS_DEBUG
@@ -632,6 +642,238 @@ __global__ void __launch_bounds__( LN_WARPS * 32, 8 ) k_lines( rc_work_t w )
 		if( novf ) atomicAdd( &w.counters[RC_CTR_OVERFLOW_EVENTS], (unsigned long long)novf );
 		if( nserial ) atomicAdd( &w.counters[RC_CTR_SERIAL_LINES], (unsigned long long)nserial );
 		if( nsorted ) atomicAdd( &w.counters[RC_CTR_SORTED_LINES], (unsigned long long)nsorted );
+	}
+}
+
+/*
+ * rc_replay_warp for lines whose band numbers more surfaces than a lane can keep in registers (up to 64 words = 2047
+ * band-local surfaces).  The set lives in shared memory (sbits) with a 64-bit summary (bit w = word w is not empty); a
+ * round of 32 events touches at most 32 different words, and only those need the XOR scan: for every touched word
+ * (uniform loop over the group leaders) all lanes scan the toggles that fall into it, which gives every lane that
+ * word's state after its own event; the lowest surface outside the touched words comes from the summary.  The rest -
+ * who is on top before and after every event, span ends, compaction - is rc_replay_warp's.
+ */
+__device__ __forceinline__ int32_t rc_replay_sparse( const unsigned long long *keys, int32_t n, int32_t head_iu, int32_t tail_u,
+	const uint16_t *bsurf, rc_span_t *spans, uint32_t *sbits, int32_t nwords, int lane )
+{
+	for( int32_t k = lane; k < nwords; k += 32 ) sbits[k] = 0;
+	__syncwarp();
+	unsigned long long summ = 0ull;
+	int32_t top_carry = 0, last_u = head_iu, nspans = 0;
+	const uint32_t lt = ( 1u << lane ) - 1u;
+	const int32_t INF = 0x7FFFFFFF;
+
+	for( int32_t c0 = 0; c0 < n; c0 += 32 )
+	{
+		const int32_t i = c0 + lane;
+		const unsigned long long key = i < n ? keys[i] : 0ull;
+		const int32_t u = (int32_t)((uint32_t)( key >> 32 ) ^ 0x80000000u );
+		const uint32_t both = (uint32_t)key;
+		const bool valid = i < n && u <= tail_u;
+		const int32_t iu = u >> 20;
+		const uint32_t trail = both >> 16, lead = both & 0xFFFFu;
+		const bool is_lead = lead != 0;
+		const int32_t s = (int32_t)( is_lead ? lead : trail );
+		const uint32_t bit = 1u << ( s & 31 );
+		const int32_t wsel = valid ? ( s >> 5 ) : -1;
+		bool exc = valid && (( trail != 0 && lead != 0 ) || wsel >= nwords );
+
+		/* leaders: the first lane of every group of lanes whose event falls into the same word */
+		const uint32_t peers = __match_any_sync( 0xFFFFFFFFu, wsel );
+		uint32_t leaders = __ballot_sync( 0xFFFFFFFFu, valid && ( __ffs( (int)peers ) - 1 ) == lane );
+		unsigned long long touched = 0ull;
+		int32_t top_t = INF;  /* lowest surface among the touched words, after this lane's event */
+		uint32_t mine = 0;
+		while( leaders )
+		{
+			const int L = __ffs( (int)leaders ) - 1;
+			leaders &= leaders - 1;
+			const int32_t wd = __shfl_sync( 0xFFFFFFFFu, wsel, L );
+			uint32_t x = wsel == wd ? bit : 0u;
+#pragma unroll
+			for( int d = 1; d < 32; d <<= 1 )
+			{
+				const uint32_t o = __shfl_up_sync( 0xFFFFFFFFu, x, d );
+				if( lane >= d ) x ^= o;
+			}
+			x ^= sbits[wd < nwords ? wd : 0]; /* the word after this lane's event (wd >= nwords: the line goes to the serial replay below) */
+			if( wsel == wd ) mine = x;
+			if( x )
+			{
+				const int32_t low = ( wd << 5 ) + __ffs( (int)x ) - 1;
+				if( low < top_t ) top_t = low;
+			}
+			touched |= 1ull << wd;
+			const uint32_t last = __shfl_sync( 0xFFFFFFFFu, x, 31 );
+			__syncwarp();
+			if( lane == 0 && wd < nwords ) sbits[wd] = last;
+			if( last ) summ |= 1ull << wd; else summ &= ~( 1ull << wd );
+		}
+		__syncwarp();
+		/* lowest surface in the words this round did not touch (their state is the one before the round) */
+		int32_t top_u = INF;
+		{
+			/* summ was updated for the touched words only: the untouched bits are still the old ones */
+			const unsigned long long mu = summ & ~touched;
+			if( mu )
+			{
+				const int32_t wu = __ffsll( (long long)mu ) - 1;
+				top_u = ( wu << 5 ) + __ffs( (int)sbits[wu] ) - 1;
+			}
+		}
+		int32_t top_after = top_t < top_u ? top_t : top_u;
+		if( top_after == INF ) top_after = 0;
+		/* lanes past the last valid event: the state after the last valid one */
+		/* leading edge: the bit must have been clear (now set); trailing edge: set (now clear) */
+		exc = exc || ( valid && ((( mine & bit ) != 0 ) != is_lead ));
+		if( __ballot_sync( 0xFFFFFFFFu, exc ))
+			return -1;
+
+		int32_t top_before = __shfl_up_sync( 0xFFFFFFFFu, top_after, 1 );
+		if( lane == 0 ) top_before = top_carry;
+		const bool brk = valid && ( is_lead ? ( top_before == 0 || s < top_before ) : ( s == top_before ));
+
+		int32_t m = brk ? iu : (int32_t)0x80000000;
+#pragma unroll
+		for( int d = 1; d < 32; d <<= 1 )
+		{
+			const int32_t o = __shfl_up_sync( 0xFFFFFFFFu, m, d );
+			if( lane >= d && o > m ) m = o;
+		}
+		int32_t prev = __shfl_up_sync( 0xFFFFFFFFu, m, 1 );
+		if( lane == 0 || prev < last_u ) prev = last_u;
+		const bool emit = brk && iu > prev;
+		const uint32_t em = __ballot_sync( 0xFFFFFFFFu, emit );
+		if( emit )
+		{
+			rc_span_t sp;
+			sp.surf = bsurf[top_before]; sp.u = (int16_t)prev; sp.count = (int16_t)( iu - prev );
+			spans[nspans + __popc( em & lt )] = sp;
+		}
+		nspans += __popc( em );
+		top_carry = __shfl_sync( 0xFFFFFFFFu, top_after, 31 );
+		const int32_t mlast = __shfl_sync( 0xFFFFFFFFu, m, 31 );
+		if( mlast > last_u ) last_u = mlast;
+	}
+	const int32_t iu = tail_u >> 20;
+	if( iu > last_u )
+	{
+		if( lane == 0 )
+		{
+			rc_span_t sp;
+			sp.surf = bsurf[top_carry]; sp.u = (int16_t)last_u; sp.count = (int16_t)( iu - last_u );
+			spans[nspans] = sp;
+		}
+		nspans++;
+	}
+	return nspans;
+}
+
+/*
+ * The lines k_lines leaves alone (RC_LINE_WIDE: up to WD_SORTCAP events, up to 2047 band-local surfaces - the horizon of
+ * a 1080p view down a long row of rooms): one block per line, lines drawn from a cursor over k_events' list.  Keys are
+ * sorted in shared memory by the whole block (bitonic network; k_events' presort leaves little to do but an unstaged
+ * band arrives unsorted), one warp replays them (rc_replay_sparse); what neither takes is replayed serially.
+ */
+__global__ void __launch_bounds__( WD_THREADS ) k_lines_wide( rc_work_t w )
+{
+	__shared__ __align__( 16 ) unsigned long long s_keys[WD_SORTCAP];
+	__shared__ uint32_t s_bits[SP_BITWORDS + 1];
+	__shared__ int32_t s_item, s_unsorted, s_nsp;
+	const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+	const int32_t nwide = *w.wide_count;
+	for( ;; )
+	{
+		__syncthreads();
+		if( t == 0 ) { s_item = atomicAdd( w.line_cursor + 2, 1 ); s_unsorted = 0; s_nsp = -1; }
+		__syncthreads();
+		const int32_t item = s_item;
+		if( item >= nwide )
+			break;
+		const int32_t line = w.wide_list[item];
+		const int32_t view = line / w.height;
+		const rc_lineinfo_t li = w.lineinfo[line];
+		const int32_t n = li.nsp & ~( RC_LINE_WIDE | RC_LINE_DONE );
+		if( li.ofs < 0 || ( li.nsp & RC_LINE_DONE ))
+			continue;
+		const rc_view_t *vw = &w.views[view];
+		const int32_t x0 = vw->vrect[0], vw_w = vw->vrect[2];
+		unsigned long long *slice = w.events + (size_t)view * w.view_events + li.ofs;
+		const int32_t bandix = view * w.nbands + ( line - view * w.height ) / SP_LINES;
+		const uint16_t *bsurf = w.bandsurf + (size_t)bandix * ( (size_t)w.max_cands + 2 );
+		const int32_t nwords = ( w.bandnloc[bandix] + 32 ) >> 5;
+		const int32_t tail_u = (( x0 + vw_w ) << 20 ) + 0xFFFFF;
+		const unsigned long long *sorted = s_keys;
+		if( n <= WD_SORTCAP )
+		{
+			int32_t npow = 64;
+			while( npow < n ) npow <<= 1;
+			bool uns = false;
+			for( int32_t i = t; i < npow; i += WD_THREADS )
+			{
+				const unsigned long long v = i < n ? slice[i] : ~0ull;
+				s_keys[i] = v;
+				uns = uns || ( i + 1 < n && v > slice[i + 1] );
+			}
+			if( uns ) s_unsorted = 1;
+			__syncthreads();
+			if( s_unsorted )
+				for( int32_t k = 2; k <= npow; k <<= 1 )
+					for( int32_t j = k >> 1; j > 0; j >>= 1 )
+					{
+						for( int32_t pr = t; pr < ( npow >> 1 ); pr += WD_THREADS )
+						{
+							const int32_t a = (( pr & ~( j - 1 )) << 1 ) | ( pr & ( j - 1 )), b = a + j;
+							const unsigned long long va = s_keys[a], vb = s_keys[b];
+							if(( va > vb ) == (( a & k ) == 0 )) { s_keys[a] = vb; s_keys[b] = va; }
+						}
+						__syncthreads();
+					}
+		}
+		else
+		{
+			/* beyond the shared-memory sorter: serial insertion sort in place, replayed from HBM */
+			if( t == 0 )
+				for( int32_t i = 1; i < n; i++ )
+				{
+					const unsigned long long key = slice[i];
+					int32_t j = i - 1;
+					while( j >= 0 && slice[j] > key ) { slice[j + 1] = slice[j]; j--; }
+					slice[j + 1] = key;
+				}
+			sorted = slice;
+			__syncthreads();
+		}
+		if( warp == 0 )
+		{
+			int32_t nsp = -1;
+			if( sorted == s_keys && nwords <= SP_BITWORDS )
+				nsp = rc_replay_sparse( s_keys, n, x0, tail_u, bsurf, reinterpret_cast<rc_span_t *>( slice ), s_bits, nwords, lane );
+			if( nsp < 0 )
+			{
+				uint32_t *bits = nwords <= SP_BITWORDS ? s_bits : w.scanbits + ( (size_t)LN_GRID * LN_WARPS - 1 - ( blockIdx.x % ( LN_GRID * LN_WARPS ))) * (size_t)w.scanbits_words;
+				for( int32_t k = lane; k < nwords; k += 32 ) bits[k] = 0;
+				__syncwarp();
+				if( lane == 0 )
+				{
+					int32_t exc[2 * SP_EXCCAP];
+					int32_t ovf = 0;
+					nsp = rc_generate_spans_bits( sorted, n, x0, tail_u, bits, nwords, exc, SP_EXCCAP, reinterpret_cast<rc_span_t *>( slice ), n + 1, &ovf );
+					if( ovf ) atomicAdd( &w.counters[RC_CTR_OVERFLOW_EVENTS], 1ull );
+					atomicAdd( &w.counters[RC_CTR_SERIAL_LINES], 1ull );
+				}
+				nsp = __shfl_sync( 0xFFFFFFFFu, nsp, 0 );
+				__syncwarp();
+				rc_span_t *sp = reinterpret_cast<rc_span_t *>( slice );
+				for( int32_t k = lane; k < nsp; k += 32 ) sp[k].surf = bsurf[sp[k].surf];
+			}
+			if( lane == 0 )
+			{
+				w.lineinfo[line].nsp = nsp | RC_LINE_DONE;
+				atomicAdd( &w.counters[RC_CTR_SPANS], (unsigned long long)nsp );
+				atomicAdd( &w.counters[RC_CTR_WIDE_LINES], 1ull );
+			}
+		}
 	}
 }
 

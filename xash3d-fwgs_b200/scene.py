@@ -35,7 +35,8 @@ class RefViewpass(C.Structure):
 assert C.sizeof(RefViewpass) == 56
 
 CTR_NAMES = ["views", "pixels", "cands", "surfs", "edges", "spans", "cache_blocks", "cache_texels",
-             "overflow_edges", "overflow_events", "overflow_stack", "overflow_cands", "serial_lines", "sorted_lines", "unstaged_bands"]
+             "overflow_edges", "overflow_events", "overflow_stack", "overflow_cands", "serial_lines", "sorted_lines", "unstaged_bands",
+             "max_cands", "max_edges", "max_band_events", "overflow_cache", "tris", "tri_pixels", "wide_lines", "overflow_fix", "fixed_faces"]
 
 
 @functools.lru_cache(maxsize=8)
