@@ -8,4 +8,4 @@ INC="-Ioracle/shim -Iinclude -Ixash3d-fwgs_b200/csrc -I$R/engine -I$R/engine/com
 mkdir -p xash3d-fwgs_b200/build
 gcc -std=gnu11 -O2 -g -fPIC -Wall -Wno-unused-function -fvisibility=hidden -ffp-contract=off $DEF $INC -c xash3d-fwgs_b200/csrc/rc_host.c -o xash3d-fwgs_b200/build/rc_host.o
 g++ -std=c++17 -O2 -g -fPIC -ffp-contract=off -Wall -Wno-unused-function -Ixash3d-fwgs_b200/csrc -c tests/emu/rc_emu.cpp -o xash3d-fwgs_b200/build/rc_emu.o
-g++ -shared xash3d-fwgs_b200/build/rc_emu.o xash3d-fwgs_b200/build/rc_host.o -lm -o tests/emu/libref_cuda_emu.so
+g++ -shared xash3d-fwgs_b200/build/rc_emu.o xash3d-fwgs_b200/build/rc_host.o xash3d-fwgs_b200/build/public_xash3d_mathlib.o xash3d-fwgs_b200/build/public_matrixlib.o -lm -o tests/emu/libref_cuda_emu.so

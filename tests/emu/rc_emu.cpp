@@ -16,6 +16,7 @@
 
 #include "rc_dev.h"
 #include "rc_core.h"
+#include "rc_tri.h"
 
 namespace {
 struct Emu
@@ -26,6 +27,8 @@ struct Emu
 	std::vector<float> verts; std::vector<uint8_t> visdata, lightdata;
 	std::vector<rc_texture_t> textures; std::vector<uint16_t> texels, colormap, lightgamma, cache;
 	std::vector<int32_t> sintable, sedgepartner; std::vector<float> sedgeverts;
+	std::vector<uint16_t> alphamap; std::vector<uint8_t> addmap, modmap;
+	std::vector<rc_item_t> items; std::vector<rc_corner_t> corners; std::vector<rc_sortent_t> sortents;
 	int32_t styles[256];
 	struct Key { int32_t texnum; int32_t light[4]; bool valid; };
 	std::vector<Key> cachekey;
@@ -129,6 +132,105 @@ int rc_dev_update_surface_texnums( const int32_t *texnum, int n )
 {
 	for( int i = 0; i < n && i < (int)E.surfaces.size(); i++ ) E.surfaces[i].texnum = texnum[i];
 	return 0;
+}
+
+int rc_dev_upload_blendluts( const uint16_t *alphamap, const uint8_t *addmap, const uint8_t *modmap )
+{
+	E.alphamap.assign( alphamap, alphamap + 3 * 1024 * 256 );
+	E.addmap.assign( addmap, addmap + 65536 ); E.modmap.assign( modmap, modmap + 65536 );
+	return 0;
+}
+
+int rc_dev_set_items( const rc_item_t *items, int nitems, const rc_corner_t *corners, int ncorners, const rc_sortent_t *sortents, int nsortents )
+{
+	E.items.assign( items, items + nitems ); E.corners.assign( corners, corners + ncorners ); E.sortents.assign( sortents, sortents + nsortents );
+	return 0;
+}
+
+/* one polygon fan of the triangle rasteriser, scanline by scanline (what the kernels do per row / per pixel) */
+static void emu_draw_poly( const rc_item_t *it, const rc_fv_t *poly, int k, uint16_t *color, int16_t *zb, int width )
+{
+	rc_blendluts_t L = { E.colormap.data(), E.alphamap.data(), E.addmap.data(), E.modmap.data() };
+	const uint16_t *skin = E.texels.data() + it->tex_ofs;
+	for( int i = 1; i < k - 1; i++ )
+	{
+		rc_trisetup_t ts;
+		if( !rc_tri_setup( &poly[0], &poly[i], &poly[i + 1], it->skinwidth, it->skinheight, &ts ))
+			continue;
+		E.counters[RC_CTR_TRIS]++;
+		int32_t y0;
+		const int32_t nrows = rc_tri_rows( &ts, &y0 );
+		for( int32_t r = 0; r < nrows; r++ )
+		{
+			rc_trirow_t row;
+			rc_tri_row( &ts, r, &row );
+			if( row.count <= 0 || !rc_tri_row_inbounds( &ts, &row ))
+				continue;
+			for( int32_t p = 0; p < row.count; p++ )
+			{
+				const size_t px = (size_t)( y0 + r ) * width + row.x + p;
+				const uint32_t src = skin[rc_tri_texel( &ts, &row, p )];
+				const int32_t light = (int32_t)((uint32_t)row.l + (uint32_t)p * (uint32_t)ts.lstepx );
+				const int32_t zi = (int32_t)((uint32_t)row.zi + (uint32_t)p * (uint32_t)ts.zistepx );
+				rc_tri_shade( &L, it->drawer, (uint32_t)it->color, (uint32_t)it->alpha, src, light, zi, &color[px], &zb[px] );
+				E.counters[RC_CTR_TRI_PIXELS]++;
+			}
+		}
+	}
+}
+
+static void emu_draw_items( const rc_view_t *vw, uint16_t *color, int16_t *zb, int width )
+{
+	if( E.items.empty() || !color || !zb )
+		return;
+	/* item order: fixed items as listed; the translucent entities in R_TransEntityCompare's order for this view */
+	std::vector<int> order;
+	std::vector<int> ents( E.sortents.size());
+	for( size_t i = 0; i < ents.size(); i++ ) ents[i] = (int)i;
+	std::vector<float> dist( E.sortents.size());
+	for( size_t i = 0; i < ents.size(); i++ )
+	{
+		const rc_sortent_t &se = E.sortents[i];
+		float v[3] = { vw->origin[0] - se.center[0], vw->origin[1] - se.center[1], vw->origin[2] - se.center[2] };
+		dist[i] = se.use_dist ? rc_dot3( v, v ) : 1000000000.0f;
+	}
+	std::stable_sort( ents.begin(), ents.end(), [&]( int a, int b ) {
+		if( dist[a] != dist[b] ) return dist[a] > dist[b];
+		return E.sortents[a].rank < E.sortents[b].rank; } );
+	bool trans_done = false;
+	for( size_t i = 0; i < E.items.size(); i++ )
+	{
+		if( E.items[i].sortent < 0 ) { order.push_back( (int)i ); continue; }
+		if( trans_done ) continue;
+		trans_done = true;
+		for( int e : ents )
+			for( size_t j = 0; j < E.items.size(); j++ )
+				if( E.items[j].sortent == e ) order.push_back( (int)j );
+	}
+	for( int idx : order )
+	{
+		const rc_item_t *it = &E.items[idx];
+		if( it->tex_ofs < 0 ) continue;
+		rc_fv_t poly[8];
+		if( it->kind == RC_ITEM_SPRITE )
+		{
+			rc_corner_t q[4];
+			if( !rc_sprite_corners( vw, it, q )) continue;
+			int k = rc_view_triangle( vw, &q[0], &q[1], &q[2], poly );
+			if( k ) emu_draw_poly( it, poly, k, color, zb, width );
+			k = rc_view_triangle( vw, &q[0], &q[2], &q[3], poly );
+			if( k ) emu_draw_poly( it, poly, k, color, zb, width );
+		}
+		else if( it->kind == RC_ITEM_TRIS )
+		{
+			for( int t = 0; t < it->count; t++ )
+			{
+				const rc_corner_t *c = &E.corners[it->first + 3 * t];
+				int k = rc_view_triangle( vw, &c[0], &c[1], &c[2], poly );
+				if( k ) emu_draw_poly( it, poly, k, color, zb, width );
+			}
+		}
+	}
 }
 
 int rc_dev_set_lightstyles( const int32_t *values ) { memcpy( E.styles, values, sizeof( E.styles )); return 0; }
@@ -279,6 +381,7 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 				}
 			}
 		}
+		emu_draw_items( vw, color, zb, width );
 		E.vsurfs[vi] = surfs; E.vedges[vi] = edges;
 		E.counters[RC_CTR_VIEWS]++; E.counters[RC_CTR_PIXELS] += (uint64_t)vw_w * vw_h;
 	}

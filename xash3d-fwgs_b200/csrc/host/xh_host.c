@@ -16,6 +16,7 @@
 
 #include "xh_internal.h"
 #include "pm_defs.h"
+#include "sprite.h"
 
 xh_state_t xh;
 
@@ -255,7 +256,8 @@ static void xh_SW_UnlockBuffer( void ) {}
 static void xh_R_StoreEfrags( struct efrag_s **pp, int framecount ) { (void)pp; (void)framecount; }
 static void xh_CL_DrawEFX( float time, qboolean trans ) { (void)time; (void)trans; xh.callbacks++; }
 static struct cl_entity_s *xh_R_BeamGetEntity( int i ) { (void)i; return NULL; }
-static void *xh_Mod_Extradata( int type, model_t *m ) { (void)type; return m ? m->cache.data : NULL; }
+/* engine/common/model.c Mod_Extradata: the cache data of a model of the asked-for type only */
+static void *xh_Mod_Extradata( int type, model_t *m ) { return ( m && (int)m->type == type ) ? m->cache.data : NULL; }
 static int xh_GL_SetAttribute( int a, int v ) { (void)a; (void)v; return 0; }
 static int xh_GL_GetAttribute( int a, int *v ) { (void)a; if( v ) *v = 0; return 0; }
 static void *xh_GL_GetProcAddress( const char *n ) { (void)n; return NULL; }
@@ -301,6 +303,8 @@ static intptr_t (*const xh_stubs[XH_NSTUBS])( void ) = {
 	S10( 1 ) S10( 2 ) S10( 3 ) S10( 4 ) S10( 5 ) S10( 6 ) S10( 7 ) S10( 8 ) S10( 9 ) S10( 10 ) S10( 11 )
 	S1( 120 ) S1( 121 ) S1( 122 ) S1( 123 ) S1( 124 ) S1( 125 ) S1( 126 ) S1( 127 )
 };
+
+static mspriteframe_t *xh_R_GetSpriteFrame( const model_t *pModel, int frame, float yaw );
 
 static void xh_fill_engfuncs( ref_api_t *e )
 {
@@ -373,7 +377,7 @@ static void xh_fill_engfuncs( ref_api_t *e )
 	e->pfnPlayerInfo = (void *)xh_null_ptr;
 	e->pfnGetPlayerState = (void *)xh_null_ptr;
 	e->GetDefaultSprite = (void *)xh_null_ptr;
-	e->R_GetSpriteFrame = (void *)xh_null_ptr;
+	e->R_GetSpriteFrame = (void *)xh_R_GetSpriteFrame;
 	e->R_StudioGetAnim = (void *)xh_null_ptr;
 	e->CL_AllocElight = (void *)xh_null_ptr;
 	e->EV_TraceSurface = (void *)xh_null_ptr;
@@ -576,7 +580,85 @@ int xh_set_dlight( int i, const float *origin, float radius, int r, int g, int b
 	return 0;
 }
 
-void xh_clear_scene( void ) { xh.ref.R_ClearScene(); }
+void xh_clear_scene( void ) { xh.ref.R_ClearScene(); xh.num_entities = 1; }
+
+/* ------------------------------------------------------------------ */
+/* sprite and studio models (engine/common/mod_sprite.c, mod_studio.c)  */
+
+static mspriteframe_t *xh_R_GetSpriteFrame( const model_t *pModel, int frame, float yaw )
+{
+	(void)yaw;
+	msprite_t *psprite = pModel ? (msprite_t *)pModel->cache.data : NULL;
+	if( !psprite ) return NULL;
+	if( frame < 0 || frame >= psprite->numframes ) frame = 0;
+	return psprite->frames[frame].frameptr; /* SPR_SINGLE frames only */
+}
+
+static model_t *xh_new_model( const char *name, modtype_t type )
+{
+	if( xh.cl.nummodels + 1 >= MAX_MODELS ) return NULL;
+	model_t *m = calloc( 1, sizeof( *m ));
+	strncpy( m->name, name, sizeof( m->name ) - 1 );
+	m->type = type;
+	m->needload = 1; /* NL_PRESENT */
+	xh.cl.models[++xh.cl.nummodels] = m;
+	return m;
+}
+
+/* a one-frame sprite model from an RGBA image: what Mod_LoadSpriteModel leaves in model_t (msprite_t with SPR_SINGLE
+ * frames whose textures went through the renderer's GL_LoadTexture); returns the model index */
+int xh_create_sprite( const char *name, int w, int h, const void *rgba, int type, int texformat, int texflags )
+{
+	model_t *m = xh_new_model( name, mod_sprite );
+	if( !m ) return -1;
+	msprite_t *ps = calloc( 1, sizeof( *ps ));
+	mspriteframe_t *fr = calloc( 1, sizeof( *fr ));
+	ps->type = (short)type; ps->texFormat = (short)texformat;
+	ps->maxwidth = w; ps->maxheight = h; ps->numframes = 1;
+	ps->radius = (int)sqrt((double)(( w >> 1 ) * ( w >> 1 ) + ( h >> 1 ) * ( h >> 1 )));
+	fr->width = w; fr->height = h;
+	fr->up = (float)( h / 2 ); fr->left = (float)( -( w / 2 )); fr->down = fr->up - h; fr->right = w + fr->left;
+	char texname[128];
+	snprintf( texname, sizeof( texname ), "#%s(frame0)", name );
+	fr->gl_texturenum = xh.ref.GL_CreateTexture( texname, w, h, rgba, texflags );
+	ps->frames[0].type = SPR_SINGLE; ps->frames[0].frameptr = fr;
+	m->cache.data = ps;
+	m->mins[0] = m->mins[1] = -w * 0.5f; m->maxs[0] = m->maxs[1] = w * 0.5f;
+	m->mins[2] = -h * 0.5f; m->maxs[2] = h * 0.5f;
+	m->numframes = 1;
+	xh.ref.Mod_ProcessRenderData( m, true, NULL, 0 );
+	return xh.cl.nummodels;
+}
+
+/* ip: modelindex, rendermode, renderamt, r, g, b, renderfx, frame, sequence, body, skin, movetype, aiment; fp: origin[3], angles[3], scale, framerate, animtime */
+int xh_add_entity( const int *ip, const float *fp )
+{
+	const int modelindex = ip[0];
+	if( modelindex <= 0 || modelindex > xh.cl.nummodels || !xh.cl.models[modelindex] ) return -1;
+	if( xh.num_entities >= (int)xh.max_entities ) return -1;
+	if( xh.num_entities < 1 ) xh.num_entities = 1; /* entity 0 is the world */
+	int idx = xh.num_entities++;
+	cl_entity_t *e = &xh.entities[idx];
+	memset( e, 0, sizeof( *e ));
+	e->index = idx;
+	e->model = xh.cl.models[modelindex];
+	e->curstate.modelindex = modelindex;
+	e->curstate.rendermode = ip[1]; e->curstate.renderamt = ip[2];
+	e->curstate.rendercolor.r = (byte)ip[3]; e->curstate.rendercolor.g = (byte)ip[4]; e->curstate.rendercolor.b = (byte)ip[5];
+	e->curstate.renderfx = ip[6]; e->curstate.frame = (float)ip[7];
+	e->curstate.sequence = ip[8]; e->curstate.body = ip[9]; e->curstate.skin = ip[10];
+	e->curstate.movetype = ip[11]; e->curstate.aiment = ip[12];
+	e->curstate.scale = fp[6]; e->curstate.framerate = fp[7]; e->curstate.animtime = fp[8];
+	for( int i = 0; i < 3; i++ )
+	{
+		e->origin[i] = e->curstate.origin[i] = e->baseline.origin[i] = fp[i];
+		e->angles[i] = e->curstate.angles[i] = fp[3 + i];
+		e->latched.prevorigin[i] = fp[i]; e->latched.prevangles[i] = fp[3 + i];
+	}
+	e->latched.prevanimtime = e->curstate.animtime;
+	e->latched.prevsequence = e->curstate.sequence;
+	return xh.ref.R_AddEntity( e, ET_NORMAL ) ? idx : -2;
+}
 
 int xh_add_brush_entity( int modelindex, const float *origin, const float *angles, int rendermode, int renderamt )
 {

@@ -27,6 +27,10 @@ int rc_dev_upload_textures( const rc_texture_t *tex, int ntex, const uint16_t *t
 int rc_dev_upload_scene( const rc_scene_t *sc, size_t cache_texels );
 /* texture number per surface after R_TextureAnimation (only changes when animated textures flip) */
 int rc_dev_update_surface_texnums( const int32_t *texnum, int n );
+/* blend tables of R_BuildBlendMaps (ref/soft/r_glblit.c:411-520): alphamap[3 * 1024 * 256] u16, addmap / modmap[65536] u8 */
+int rc_dev_upload_blendluts( const uint16_t *alphamap, const uint8_t *addmap, const uint8_t *modmap );
+/* the entities of the next batches as ordered draw items (rc_shared.h); nitems = 0: none */
+int rc_dev_set_items( const rc_item_t *items, int nitems, const rc_corner_t *corners, int ncorners, const rc_sortent_t *sortents, int nsortents );
 /* g_lightstylevalue[256] for the next batch (ref/common/ref_light.c:30-87) */
 int rc_dev_set_lightstyles( const int32_t *values );
 /* the active dynamic lights of the next batches (R_PushDlights, ref/common/ref_light.c:170: die >= time, radius != 0);

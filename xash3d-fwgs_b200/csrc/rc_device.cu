@@ -593,6 +593,12 @@ struct Dev
 	bool have_batch = false;
 	void *d_flush = nullptr;
 
+	/* entities of the next batches */
+	uint16_t *d_alphamap = nullptr; uint8_t *d_addmap = nullptr, *d_modmap = nullptr;
+	rc_item_t *d_items = nullptr; rc_corner_t *d_corners = nullptr; rc_sortent_t *d_sortents = nullptr;
+	int nitems = 0, ncorners = 0, nsortents = 0;
+	std::vector<rc_item_t> h_items;
+
 	/* dynamic lights of the next batch */
 	rc_dlight_t *d_dlights = nullptr;
 	uint32_t *d_dlightbits = nullptr;
@@ -958,7 +964,7 @@ void rc_dev_shutdown( void )
 	cudaDeviceSynchronize();
 	free_batch();
 	/* everything rc_dev_init / the uploads created, so that R_Shutdown + R_Init (vid_restart) starts clean */
-	void **ptrs[] = { (void **)&D.d_display, (void **)&D.d_screenmap, (void **)&D.d_dlights, (void **)&D.d_dlightbits,
+	void **ptrs[] = { (void **)&D.d_alphamap, (void **)&D.d_addmap, (void **)&D.d_modmap, (void **)&D.d_items, (void **)&D.d_corners, (void **)&D.d_sortents, (void **)&D.d_display, (void **)&D.d_screenmap, (void **)&D.d_dlights, (void **)&D.d_dlightbits,
 		(void **)&D.d_colormap, (void **)&D.d_lightgamma, (void **)&D.d_sintable, (void **)&D.d_textures, (void **)&D.d_texels,
 		(void **)&D.d_styles, (void **)&D.d_keys, (void **)&D.d_need, (void **)&D.d_list, (void **)&D.d_nlist,
 		(void **)&D.d_counters, &D.d_flush };
@@ -966,6 +972,7 @@ void rc_dev_shutdown( void )
 	for( void *&p : D.d_scene ) { if( p ) cudaFree( p ); p = nullptr; }
 	if( D.h_counters ) { cudaFreeHost( D.h_counters ); D.h_counters = nullptr; }
 	D.cap_cands = D.cap_edges = D.cap_blk_events = 0; D.caps_dirty = false;
+	D.nitems = D.ncorners = D.nsortents = 0; D.h_items.clear();
 	D.display_bytes = 0; D.ndlights = 0; D.screen_bpp = 0; D.cache_texels = 0; D.ntextures = 0;
 	D.sc = rc_scene_t{}; D.h_surfaces.clear(); D.h_textures.clear();
 	cudaStream_t *streams[] = { &D.stream, &D.copy };
@@ -1094,6 +1101,28 @@ int rc_dev_upload_scene( const rc_scene_t *sc, size_t cache_texels )
 	D.ndlights = 0;
 	if( upload( &D.d_need, (const uint32_t *)nullptr, RC_MAX_SLICES * ( nslots / 32 + 2 )) != 0 ) return -1;
 	if( upload( &D.d_list, (const int32_t *)nullptr, RC_MAX_SLICES * nslots ) != 0 ) return -1;
+	return 0;
+}
+
+int rc_dev_upload_blendluts( const uint16_t *alphamap, const uint8_t *addmap, const uint8_t *modmap )
+{
+	if( upload( &D.d_alphamap, alphamap, (size_t)3 * 1024 * 256 ) != 0 ) return -1;
+	if( upload( &D.d_addmap, addmap, 65536 ) != 0 ) return -1;
+	if( upload( &D.d_modmap, modmap, 65536 ) != 0 ) return -1;
+	return 0;
+}
+
+int rc_dev_set_items( const rc_item_t *items, int nitems, const rc_corner_t *corners, int ncorners, const rc_sortent_t *sortents, int nsortents )
+{
+	if( !nitems && !D.nitems ) return 0;
+	CK( cudaStreamSynchronize( D.stream ));
+	D.nitems = nitems; D.nsortents = nsortents; D.ncorners = ncorners;
+	if( !nitems ) return 0;
+	if( upload( &D.d_items, items, (size_t)nitems ) != 0 ) return -1;
+	if( upload( &D.d_corners, corners, (size_t)ncorners ) != 0 ) return -1;
+	if( upload( &D.d_sortents, sortents, (size_t)nsortents ) != 0 ) return -1;
+	D.h_items.assign( items, items + nitems );
+	D.h2d_bytes += sizeof( rc_item_t ) * (size_t)nitems + sizeof( rc_corner_t ) * (size_t)ncorners + sizeof( rc_sortent_t ) * (size_t)nsortents;
 	return 0;
 }
 

@@ -31,12 +31,17 @@
 #include "com_strings.h"
 #include "lightstyle.h"
 #include "xash3d_mathlib.h"
+#include "sprite.h"
+#include "studio.h"
+#include "triangleapi.h"
+#include "entity_types.h"
 
 #include "rc_dev.h"
 #include "ref_cuda.h"
 
 #define RC_MAX_TEXTURES 8192
 #define RC_MAX_QUEUED_VIEWS 16384
+#define RC_MAX_VISIBLE 2048 /* MAX_VISIBLE_PACKET */
 #define LM_SAMPLE_SIZE 16
 
 DEFINE_ENGINE_SHARED_CVAR_LIST()
@@ -97,6 +102,35 @@ static struct
 	uint         map_valid, map_bpp, map_r, map_g, map_b; /* display format the device's screen map was built for */
 	unsigned long long last_h2d;
 	char         error[512];
+
+	/* entity lists of the frame (draw_list_t, ref/soft/r_local.h; R_AddEntity, r_main.c:311) */
+	cl_entity_t *solid_ents[RC_MAX_VISIBLE], *trans_ents[RC_MAX_VISIBLE], *edge_ents[RC_MAX_VISIBLE];
+	int          num_solid, num_trans, num_edge;
+	cl_entity_t *entities; uint max_entities;
+
+	/* the immediate-mode state TriAPI / GL_Bind keep in viddef_t and r_triapi.c's statics */
+	struct
+	{
+		int      rendermode;      /* vid.rendermode */
+		int      is2d;
+		uint     alpha, color;    /* vid.alpha, vid.color */
+		uint     light;
+		short    s, t;
+		int      prim, vertcount, n;
+		int      drawer, texnum, tex_ofs, skinwidth, skinheight; /* r_affinetridesc + d_pdrawspans as GL_Bind left them */
+		float    triRGBA[4];
+		int      triRenderMode;
+		rc_corner_t triv[3];
+		float    blend;           /* tr.blend */
+	} tri;
+
+	/* draw items of the batch being prepared */
+	rc_texture_t *textab; int ntextab; /* the texture table as last sent to the device (arena offsets) */
+	rc_item_t   *items; int nitems, maxitems;
+	rc_corner_t *corners; int ncorners, maxcorners;
+	rc_sortent_t *sortents; int nsortents, maxsortents;
+	int          cur_sortent;
+	qboolean     warned[8];
 } rc;
 
 static void rc_strncpy( char *dst, const char *src, size_t n ) { strncpy( dst, src, n - 1 ); dst[n - 1] = 0; }
@@ -369,7 +403,9 @@ static void rc_sync_textures( void )
 			total += (size_t)Q_max( 1, t->width >> j ) * Q_max( 1, t->height >> j );
 		if( t->alpha_pixels ) total += (size_t)t->width * t->height;
 	}
-	rc_texture_t *tab = rc_malloc( sizeof( rc_texture_t ) * Q_max( 1, rc.numImages ));
+	rc_free( rc.textab );
+	rc_texture_t *tab = rc.textab = rc_malloc( sizeof( rc_texture_t ) * Q_max( 1, rc.numImages ));
+	rc.ntextab = rc.numImages;
 	uint16_t *arena = rc_malloc(( total + 64 ) * sizeof( uint16_t ));
 	size_t o = 0;
 	for( int i = 0; i < rc.numImages; i++ )
@@ -395,7 +431,6 @@ static void rc_sync_textures( void )
 		}
 	}
 	RC_CHECK_DEV( rc_dev_upload_textures( tab, rc.numImages, arena, total + 64 ));
-	rc_free( tab );
 	rc_free( arena );
 	rc.textures_dirty = false;
 }
@@ -753,6 +788,25 @@ static void rc_setup_view( const ref_viewpass_t *rvp, rc_view_t *v )
 	v->modelorg_t[1] = DotProduct( modelorg, vup );
 	v->modelorg_t[2] = DotProduct( modelorg, vforward );
 
+	/* R_SetUpWorldTransform (ref/soft/r_trialias.c:52): the view matrix (vright, -vup, vforward) times a translation by
+	 * -vieworigin, through the engine's own Matrix3x4_ConcatTransforms so that every product rounds as it does there */
+	{
+		matrix3x4 viewmatrix, world;
+		vec3_t zero = { 0, 0, 0 }, f, r, u;
+		AngleVectors( zero, f, r, u );
+		memset( world, 0, sizeof( world ));
+		for( int i = 0; i < 3; i++ ) { world[i][0] = f[i]; world[i][1] = -r[i]; world[i][2] = u[i]; }
+		world[0][3] = -rvp->vieworigin[0]; world[1][3] = -rvp->vieworigin[1]; world[2][3] = -rvp->vieworigin[2];
+		VectorCopy( vright, viewmatrix[0] );
+		VectorCopy( vup, viewmatrix[1] );
+		viewmatrix[1][0] = -viewmatrix[1][0]; viewmatrix[1][1] = -viewmatrix[1][1]; viewmatrix[1][2] = -viewmatrix[1][2];
+		VectorCopy( vforward, viewmatrix[2] );
+		viewmatrix[0][3] = viewmatrix[1][3] = viewmatrix[2][3] = 0;
+		matrix3x4 out;
+		Matrix3x4_ConcatTransforms( out, viewmatrix, world );
+		memcpy( v->aliastransform, out, sizeof( out ));
+	}
+
 	v->turb_phase = (int)( gp_cl->time * 20 ) & 127; /* SPEED, CYCLE */
 	v->sky_color = (int)sw_clearcolor.value & 0xFFFF;
 	v->flags = rvp->flags;
@@ -788,6 +842,463 @@ static void rc_push_dlights( void )
 	rc.had_dlights = n > 0;
 }
 
+
+static const rc_texture_t *rc_texture_entry( int texnum )
+{
+	return ( texnum > 0 && texnum < rc.ntextab && rc.images[texnum].pixels[0] ) ? &rc.textab[texnum] : NULL;
+}
+
+/* ---------------------------------------------------------------------------------------------- */
+/* blend tables: vid.addmap / modmap / alphamap of R_BuildBlendMaps (ref/soft/r_glblit.c:411-520).  A pixel_t is a
+ * 3-3-2 "major" byte over a byte of low channel bits; addmap and modmap act on major bytes (saturating add, scaled
+ * product), alphamap mixes a 10-bit screen code (major + 2 minor bits) with a major source code at 2/7, 3/7, 4/7. */
+
+static void rc_build_blendmaps( uint16_t *alphamap, uint8_t *addmap, uint8_t *modmap )
+{
+	for( uint a = 0; a < 256; a++ )
+		for( uint b = 0; b < 256; b++ )
+		{
+			const uint r1 = a >> 5, g1 = ( a >> 2 ) & 7, b1 = a & 3, r2 = b >> 5, g2 = ( b >> 2 ) & 7, b2 = b & 3;
+			addmap[b << 8 | a] = (uint8_t)( Q_min( r1 + r2, 7u ) << 5 | Q_min( g1 + g2, 7u ) << 2 | Q_min( b1 + b2, 3u ));
+			modmap[b << 8 | a] = (uint8_t)(( r1 * r2 / 7 ) << 5 | ( g1 * g2 / 7 ) << 2 | ( b1 * b2 / 3 ));
+		}
+	for( uint i = 0; i < 1024; i++ )
+	{
+		uint r1, g1, b1;
+		rc_decode565( i << 6 | 0x38, &r1, &g1, &b1 ); /* the screen colour: 10 known bits, the three below them set */
+		for( uint m2 = 0; m2 < 256; m2++ )
+		{
+			const uint r2 = ( m2 >> 5 ) << 2 | 4, g2 = (( m2 >> 2 ) & 7 ) << 3 | 3, b2 = ( m2 & 3 ) << 3 | 3; /* the source's major byte, mid-range */
+			for( uint k = 0; k < 3; k++ )
+			{
+				const uint a = k + 2;
+				const uint r = Q_min( r1 * ( 7 - a ) / 7 + r2 * a / 7, 31u ), g = Q_min( g1 * ( 7 - a ) / 7 + g2 * a / 7, 63u ), b = Q_min( b1 * ( 7 - a ) / 7 + b2 * a / 7, 31u );
+				alphamap[k << 18 | m2 << 10 | i] = rc_encode565( r, g, b ) & ~0x3f;
+			}
+		}
+	}
+}
+
+/* ---------------------------------------------------------------------------------------------- */
+/* entity lists: R_AddEntity / R_ClearScene (ref/soft/r_main.c:293-363), CL_FxBlend (:1406)           */
+
+static int rc_fx_blend( cl_entity_t *e )
+{
+	int blend = 0;
+	const float offset = ((int)e->index ) * 363.0f;
+	const int amt = e->curstate.renderamt;
+	switch( e->curstate.renderfx )
+	{
+	case kRenderFxPulseSlowWide: blend = amt + 0x40 * sin( gp_cl->time * 2 + offset ); break;
+	case kRenderFxPulseFastWide: blend = amt + 0x40 * sin( gp_cl->time * 8 + offset ); break;
+	case kRenderFxPulseSlow: blend = amt + 0x10 * sin( gp_cl->time * 2 + offset ); break;
+	case kRenderFxPulseFast: blend = amt + 0x10 * sin( gp_cl->time * 8 + offset ); break;
+	case kRenderFxFadeSlow: e->curstate.renderamt = amt > 0 ? amt - 1 : 0; blend = e->curstate.renderamt; break;
+	case kRenderFxFadeFast: e->curstate.renderamt = amt > 3 ? amt - 4 : 0; blend = e->curstate.renderamt; break;
+	case kRenderFxSolidSlow: e->curstate.renderamt = amt < 255 ? amt + 1 : 255; blend = e->curstate.renderamt; break;
+	case kRenderFxSolidFast: e->curstate.renderamt = amt < 252 ? amt + 4 : 255; blend = e->curstate.renderamt; break;
+	case kRenderFxStrobeSlow: blend = 20 * sin( gp_cl->time * 4 + offset ); blend = blend < 0 ? 0 : amt; break;
+	case kRenderFxStrobeFast: blend = 20 * sin( gp_cl->time * 16 + offset ); blend = blend < 0 ? 0 : amt; break;
+	case kRenderFxStrobeFaster: blend = 20 * sin( gp_cl->time * 36 + offset ); blend = blend < 0 ? 0 : amt; break;
+	case kRenderFxFlickerSlow: blend = 20 * ( sin( gp_cl->time * 2 ) + sin( gp_cl->time * 17 + offset )); blend = blend < 0 ? 0 : amt; break;
+	case kRenderFxFlickerFast: blend = 20 * ( sin( gp_cl->time * 16 ) + sin( gp_cl->time * 23 + offset )); blend = blend < 0 ? 0 : amt; break;
+	case kRenderFxHologram:
+	case kRenderFxDistort:
+		/* the reference fades these with the distance along the CURRENT view's forward axis; a batch has many views */
+		if( !rc.warned[0] ) { rc.warned[0] = true; gEngfuncs.Con_Reportf( "ref_cuda: kRenderFxHologram / kRenderFxDistort fade per view is not built: drawn at renderamt 180\n" ); }
+		e->curstate.renderamt = 180;
+		blend = 180;
+		break;
+	default: blend = amt; break;
+	}
+	return bound( 0, blend, 255 );
+}
+
+static qboolean rc_model_opaque( int rendermode ) { return rendermode == kRenderNormal; }
+
+/* R_GetEntityRenderMode (ref/soft/r_studio.c:2109) */
+static int rc_entity_rendermode( cl_entity_t *ent )
+{
+	model_t *model = ent->model;
+	studiohdr_t *phdr = model ? (studiohdr_t *)gEngfuncs.Mod_Extradata( mod_studio, model ) : NULL;
+	if( !phdr || !model || model->type != mod_studio )
+	{
+		if( rc_model_opaque( ent->curstate.rendermode ) && model && model->type == mod_brush && FBitSet( model->flags, MODEL_TRANSPARENT ))
+			return kRenderTransAlpha;
+		return ent->curstate.rendermode;
+	}
+	const mstudiotexture_t *ptexture = (const mstudiotexture_t *)((const byte *)phdr + phdr->textureindex );
+	int opaque = 0, trans = 0;
+	for( int i = 0; i < phdr->numtextures; i++, ptexture++ )
+	{
+		if( FBitSet( ptexture->flags, STUDIO_NF_ADDITIVE ) && !FBitSet( ptexture->flags, STUDIO_NF_CHROME )) trans++;
+		else opaque++;
+	}
+	return trans > opaque ? kRenderTransAdd : ent->curstate.rendermode;
+}
+
+static qboolean rc_opaque_entity( cl_entity_t *ent )
+{
+	if( rc_entity_rendermode( ent ) == kRenderNormal )
+	{
+		switch( ent->curstate.renderfx )
+		{
+		case kRenderFxNone: case kRenderFxDeadPlayer: case kRenderFxLightMultiplier: case kRenderFxExplode:
+			return true;
+		}
+	}
+	return false;
+}
+
+static qboolean R_AddEntity( struct cl_entity_s *clent, int type )
+{
+	if( !r_drawentities->value )
+		return false;
+	if( FBitSet( clent->curstate.effects, EF_NODRAW ))
+		return false;
+	if( !rc_model_opaque( clent->curstate.rendermode ) && rc_fx_blend( clent ) <= 0 )
+		return true; /* invisible */
+	if( type == ET_BEAM )
+	{
+		if( !rc.warned[1] ) { rc.warned[1] = true; gEngfuncs.Con_Reportf( "ref_cuda: beam entities are not drawn yet\n" ); }
+		return true;
+	}
+	if( rc_opaque_entity( clent ))
+	{
+		if( clent->model && clent->model->type == mod_brush )
+		{
+			if( rc.num_edge >= RC_MAX_VISIBLE ) return false;
+			rc.edge_ents[rc.num_edge++] = clent;
+			return true;
+		}
+		if( rc.num_solid >= RC_MAX_VISIBLE ) return false;
+		rc.solid_ents[rc.num_solid++] = clent;
+	}
+	else
+	{
+		if( rc.num_trans >= RC_MAX_VISIBLE ) return false;
+		rc.trans_ents[rc.num_trans++] = clent;
+	}
+	return true;
+}
+
+static void R_ClearScene( void ) { rc.num_solid = rc.num_trans = rc.num_edge = 0; }
+static void R_ProcessEntData( qboolean allocate, cl_entity_t *entities, unsigned int max_entities )
+{
+	rc.entities = allocate ? entities : NULL;
+	rc.max_entities = allocate ? max_entities : 0;
+}
+
+/* ---------------------------------------------------------------------------------------------- */
+/* TriAPI (ref/soft/r_triapi.c:46-261) and GL_Bind (r_image.c:43-75): the calls keep the reference's immediate-mode
+ * state; where the reference rasterises a triangle on the spot, here its three world-space corners join the batch's
+ * draw items - projection, clipping and rasterisation happen per view on the device.                                  */
+
+static void *rc_grow( void *p, int *cap, int need, size_t elem )
+{
+	if( need <= *cap ) return p;
+	int n = *cap ? *cap : 256;
+	while( n < need ) n *= 2;
+	p = gEngfuncs._Mem_Realloc( rc.pool, p, elem * n, true, __FILE__, __LINE__ );
+	*cap = n;
+	return p;
+}
+
+static rc_item_t *rc_new_item( int kind )
+{
+	rc.items = rc_grow( rc.items, &rc.maxitems, rc.nitems + 1, sizeof( rc_item_t ));
+	rc_item_t *it = &rc.items[rc.nitems++];
+	memset( it, 0, sizeof( *it ));
+	it->kind = kind;
+	it->drawer = rc.tri.drawer; it->tex_ofs = rc.tri.texnum; /* texture NUMBER here; resolved to an arena offset when the batch is sent */
+	it->skinwidth = rc.tri.skinwidth; it->skinheight = rc.tri.skinheight;
+	it->color = rc.tri.color; it->alpha = rc.tri.alpha;
+	it->sortent = rc.cur_sortent;
+	return it;
+}
+
+static void GL_SetRenderMode( int renderMode ) { rc.tri.rendermode = renderMode; }
+static void TriRenderMode( int mode ) { rc.tri.triRenderMode = rc.tri.rendermode = mode; }
+
+static void GL_Bind( int tmu, unsigned int texnum )
+{
+	(void)tmu;
+	if( texnum >= RC_MAX_TEXTURES ) texnum = 0;
+	const rc_image_t *image = &rc.images[texnum];
+	const int mode = rc.tri.rendermode;
+	rc.tri.drawer = mode == kRenderNormal ? RC_DRAW_FILL : mode == kRenderTransAdd ? RC_DRAW_ADDITIVE : mode == kRenderGlow ? RC_DRAW_GLOW
+		: image->alpha_pixels ? RC_DRAW_TEXBLEND : RC_DRAW_BLEND;
+	rc.tri.texnum = (int)texnum;
+	rc.tri.skinwidth = image->width; rc.tri.skinheight = image->height;
+}
+
+static void rc_tri_color4f( float rr, float gg, float bb, float aa )
+{
+	if( rc.tri.rendermode == kRenderTransAdd || rc.tri.rendermode == kRenderGlow )
+		rr *= aa, gg *= aa, bb *= aa;
+	rc.tri.light = ( rr + gg + bb ) * 31 / 3;
+	if( rc.tri.light > 31 ) rc.tri.light = 31;
+	if( !rc.tri.is2d && rc.tri.rendermode == kRenderNormal )
+		return;
+	rc.tri.alpha = aa * 7;
+	if( rc.tri.alpha > 7 ) rc.tri.alpha = 7;
+	if( rr == 1 && gg == 1 && bb == 1 )
+	{
+		rc.tri.color = 0xFFFF; /* COLOR_WHITE */
+		return;
+	}
+	unsigned short r = rr * 31, g = gg * 63, b = bb * 31;
+	rc.tri.color = rc_encode565( Q_min( r, 31 ), Q_min( g, 63 ), Q_min( b, 31 ));
+}
+
+static void TriColor4ub( unsigned char r, unsigned char g, unsigned char b, unsigned char a )
+{
+	rc.tri.triRGBA[0] = r * ( 1.0f / 255.0f ); rc.tri.triRGBA[1] = g * ( 1.0f / 255.0f );
+	rc.tri.triRGBA[2] = b * ( 1.0f / 255.0f ); rc.tri.triRGBA[3] = a * ( 1.0f / 255.0f );
+	rc_tri_color4f( rc.tri.triRGBA[0], rc.tri.triRGBA[1], rc.tri.triRGBA[2], 1.0f );
+}
+
+static void TriColor4f( float r, float g, float b, float a )
+{
+	if( rc.tri.triRenderMode == kRenderTransAlpha )
+		TriColor4ub( r * 255.0f, g * 255.0f, b * 255.0f, a * 255.0f );
+	else
+		rc_tri_color4f( r * a, g * a, b * a, 1.0 );
+	rc.tri.triRGBA[0] = r; rc.tri.triRGBA[1] = g; rc.tri.triRGBA[2] = b; rc.tri.triRGBA[3] = a;
+}
+
+static void TriTexCoord2f( float u, float v )
+{
+	double u1 = 0, v1 = 0;
+	u = fmodf( u, 10 );
+	v = fmodf( v, 10 );
+	if( u < 1000 && u > -1000 ) u1 = u;
+	if( v < 1000 && v > -1000 ) v1 = v;
+	while( u1 < 0 ) u1 = u1 + 1;
+	while( v1 < 0 ) v1 = v1 + 1;
+	while( u1 > 1 ) u1 = u1 - 1;
+	while( v1 > 1 ) v1 = v1 - 1;
+	rc.tri.s = rc.tri.skinwidth * bound( 0.01, u1, 0.99 );
+	rc.tri.t = rc.tri.skinheight * bound( 0.01, v1, 0.99 );
+}
+
+static void TriBegin( int primitiveCode )
+{
+	if( primitiveCode == TRI_QUADS ) primitiveCode = TRI_TRIANGLE_FAN;
+	rc.tri.prim = primitiveCode;
+	rc.tri.n = rc.tri.vertcount = 0;
+}
+static void TriEnd( void ) {}
+
+/* one assembled triangle (R_RenderTriangle's arguments) joins the current item, or opens one when the state changed */
+static void rc_tri_emit( const rc_corner_t *a, const rc_corner_t *b, const rc_corner_t *c )
+{
+	rc_item_t *it = rc.nitems ? &rc.items[rc.nitems - 1] : NULL;
+	if( !it || it->kind != RC_ITEM_TRIS || it->drawer != rc.tri.drawer || it->tex_ofs != rc.tri.texnum || it->color != (int)rc.tri.color
+		|| it->alpha != (int)rc.tri.alpha || it->sortent != rc.cur_sortent || it->first + 3 * it->count != rc.ncorners )
+	{
+		it = rc_new_item( RC_ITEM_TRIS );
+		it->first = rc.ncorners;
+	}
+	rc.corners = rc_grow( rc.corners, &rc.maxcorners, rc.ncorners + 3, sizeof( rc_corner_t ));
+	rc.corners[rc.ncorners++] = *a; rc.corners[rc.ncorners++] = *b; rc.corners[rc.ncorners++] = *c;
+	it->count++;
+}
+
+static void TriVertex3f( float x, float y, float z )
+{
+	rc_corner_t cv;
+	cv.xyz[0] = x; cv.xyz[1] = y; cv.xyz[2] = z;
+	cv.l = (int32_t)( rc.tri.light << 8 ); cv.s = rc.tri.s; cv.t = rc.tri.t;
+	rc_corner_t *triv = rc.tri.triv;
+	if( rc.tri.prim == TRI_TRIANGLES )
+	{
+		triv[rc.tri.vertcount++] = cv;
+		if( rc.tri.vertcount == 3 )
+		{
+			rc_tri_emit( &triv[0], &triv[1], &triv[2] );
+			rc.tri.vertcount = 0;
+		}
+	}
+	if( rc.tri.prim == TRI_TRIANGLE_FAN )
+	{
+		triv[rc.tri.vertcount++] = cv;
+		if( rc.tri.vertcount >= 3 )
+		{
+			rc_tri_emit( &triv[0], &triv[1], &triv[2] );
+			triv[1] = triv[2];
+			rc.tri.vertcount = 2;
+		}
+	}
+	if( rc.tri.prim == TRI_TRIANGLE_STRIP )
+	{
+		triv[rc.tri.n] = cv;
+		rc.tri.n++;
+		rc.tri.vertcount++;
+		if( rc.tri.n == 3 ) rc.tri.n = 0;
+		if( rc.tri.vertcount >= 3 )
+		{
+			if( rc.tri.vertcount & 1 ) rc_tri_emit( &triv[0], &triv[1], &triv[2] );
+			else rc_tri_emit( &triv[2], &triv[1], &triv[0] );
+		}
+	}
+}
+static void TriVertex3fv( const float *worldPnt ) { TriVertex3f( worldPnt[0], worldPnt[1], worldPnt[2] ); }
+static void TriCullFace( TRICULLSTYLE mode ) { (void)mode; }
+
+/* ---------------------------------------------------------------------------------------------- */
+/* sprites: the view-independent half of R_DrawSpriteModel (ref/soft/r_sprite.c:160-266); orientation, the quad's four
+ * corners and everything after them run per view on the device                                                       */
+
+static void rc_add_sprite( cl_entity_t *e )
+{
+	model_t *model = e->model;
+	msprite_t *psprite = (msprite_t *)model->cache.data;
+	if( !psprite )
+		return; /* R_CullSpriteModel */
+	vec3_t origin;
+	VectorCopy( e->origin, origin );
+	if( e->curstate.aiment > 0 && e->curstate.movetype == MOVETYPE_FOLLOW && rc.entities && (uint)e->curstate.aiment < rc.max_entities )
+	{
+		cl_entity_t *parent = &rc.entities[e->curstate.aiment];
+		if( parent->model )
+		{
+			if( parent->model->type == mod_studio && e->curstate.body > 0 )
+				VectorCopy( parent->attachment[bound( 1, e->curstate.body, MAXSTUDIOATTACHMENTS ) - 1], origin );
+			else VectorCopy( parent->origin, origin );
+		}
+	}
+	float scale = e->curstate.scale;
+	if( !scale ) scale = 1.0f;
+	if( e->curstate.rendermode == kRenderGlow )
+	{
+		/* R_SpriteOccluded for glow sprites traces a line per view through the engine (EV_VisTraceLine) */
+		if( !rc.warned[2] ) { rc.warned[2] = true; gEngfuncs.Con_Reportf( "ref_cuda: kRenderGlow sprites (per-view occlusion trace) are not drawn yet\n" ); }
+		return;
+	}
+	GL_SetRenderMode( e->curstate.rendermode );
+	vec3_t color;
+	if( e->curstate.rendercolor.r || e->curstate.rendercolor.g || e->curstate.rendercolor.b )
+	{
+		color[0] = (float)e->curstate.rendercolor.r * ( 1.0f / 255.0f );
+		color[1] = (float)e->curstate.rendercolor.g * ( 1.0f / 255.0f );
+		color[2] = (float)e->curstate.rendercolor.b * ( 1.0f / 255.0f );
+	}
+	else color[0] = color[1] = color[2] = 1.0f;
+	mspriteframe_t *frame = gEngfuncs.R_GetSpriteFrame( model, e->curstate.frame, e->angles[YAW] );
+	if( !frame )
+		return;
+	int type = psprite->type;
+	if( e->angles[ROLL] != 0.0f && type == SPR_FWD_PARALLEL )
+		type = SPR_FWD_PARALLEL_ORIENTED;
+	rc_tri_color4f( color[0], color[1], color[2], rc.tri.blend );
+	GL_Bind( XASH_TEXTURE0, frame->gl_texturenum );
+
+	rc_item_t *it = rc_new_item( RC_ITEM_SPRITE );
+	it->count = 2;
+	it->sprtype = type; it->light = (int32_t)( rc.tri.light << 8 );
+	VectorCopy( origin, it->origin ); VectorCopy( e->angles, it->angles );
+	it->scale = scale;
+	it->fr_up = frame->up; it->fr_down = frame->down; it->fr_left = frame->left; it->fr_right = frame->right;
+	TriTexCoord2f( 0.0f, 0.0f ); it->s0 = rc.tri.s; it->t0 = rc.tri.t;
+	TriTexCoord2f( 1.0f, 1.0f ); it->s1 = rc.tri.s; it->t1 = rc.tri.t;
+	if( type == SPR_ORIENTED )
+	{
+		vec3_t v_forward, v_right, v_up;
+		AngleVectors( e->angles, v_forward, v_right, v_up );
+		VectorScale( v_forward, 0.01f, v_forward ); /* to avoid z-fighting */
+		VectorSubtract( origin, v_forward, it->origin );
+		VectorCopy( v_right, it->vright ); VectorCopy( v_up, it->vup );
+	}
+	else if( type == SPR_FWD_PARALLEL_ORIENTED )
+	{
+		const float angle = e->angles[ROLL] * ( M_PI2 / 360.0f );
+		SinCos( angle, &it->sr, &it->cr );
+	}
+}
+
+static void rc_add_studio( cl_entity_t *e );
+
+/* R_DrawEntitiesOnList (ref/soft/r_main.c:504-635) as a list of draw items: solid studio models, solid sprites, the
+ * client's opaque triangles, then the translucent entities (each with a sort record) and the client's translucent ones */
+static void rc_build_items( void )
+{
+	rc.nitems = rc.ncorners = rc.nsortents = 0;
+	rc.cur_sortent = -1;
+	rc.tri.blend = 1.0f;
+	rc.tri.drawer = RC_DRAW_FILL;
+	GL_SetRenderMode( kRenderNormal );
+	for( int i = 0; i < rc.num_solid; i++ )
+	{
+		cl_entity_t *e = rc.solid_ents[i];
+		if( e->model && e->model->type == mod_studio )
+			rc_add_studio( e );
+	}
+	for( int i = 0; i < rc.num_solid; i++ )
+	{
+		cl_entity_t *e = rc.solid_ents[i];
+		if( e->model && e->model->type == mod_sprite )
+			rc_add_sprite( e );
+	}
+	gEngfuncs.CL_DrawEFX( gp_cl->time - gp_cl->oldtime, false );
+	gEngfuncs.pfnDrawNormalTriangles();
+	for( int i = 0; i < rc.num_trans; i++ )
+	{
+		cl_entity_t *e = rc.trans_ents[i];
+		if( !e->model )
+			continue;
+		rc.tri.blend = e->curstate.rendermode != kRenderNormal ? rc_fx_blend( e ) / 255.0f : 1.0f;
+		if( rc.tri.blend <= 0.0f )
+			continue;
+		/* R_TransEntityCompare's key for this entity */
+		rc.sortents = rc_grow( rc.sortents, &rc.maxsortents, rc.nsortents + 1, sizeof( rc_sortent_t ));
+		rc_sortent_t *se = &rc.sortents[rc.nsortents];
+		memset( se, 0, sizeof( *se ));
+		const int rendermode = rc_entity_rendermode( e );
+		vec3_t org;
+		VectorAverage( e->model->mins, e->model->maxs, org );
+		VectorAdd( e->origin, org, se->center );
+		se->use_dist = ( e->model->type != mod_brush || rendermode != kRenderTransAlpha ) ? 1 : 0;
+		se->rank = rendermode == kRenderTransTexture ? 1 : rendermode == kRenderTransAdd ? 2 : rendermode == kRenderGlow ? 3 : 0;
+		rc.cur_sortent = rc.nsortents++;
+		switch( e->model->type )
+		{
+		case mod_studio: rc_add_studio( e ); break;
+		case mod_sprite: rc_add_sprite( e ); break;
+		case mod_brush:
+			if( !rc.warned[3] ) { rc.warned[3] = true; gEngfuncs.Con_Reportf( "ref_cuda: translucent brush entities are not drawn yet\n" ); }
+			break;
+		default: break;
+		}
+	}
+	rc.cur_sortent = -1;
+	rc.tri.blend = 1.0f;
+	gEngfuncs.pfnDrawTransparentTriangles();
+	gEngfuncs.CL_DrawEFX( gp_cl->time - gp_cl->oldtime, true );
+	GL_SetRenderMode( kRenderNormal );
+	if( rc.num_edge && !rc.warned[4] ) { rc.warned[4] = true; gEngfuncs.Con_Reportf( "ref_cuda: opaque brush entities are not drawn yet\n" ); }
+
+	/* texture numbers -> texel arena offsets, triangle numbering */
+	int order = 0;
+	for( int i = 0; i < rc.nitems; i++ )
+	{
+		rc_item_t *it = &rc.items[i];
+		const rc_image_t *img = &rc.images[it->tex_ofs];
+		const rc_texture_t *t = rc_texture_entry( it->tex_ofs );
+		it->tex_ofs = t ? ( it->drawer == RC_DRAW_TEXBLEND ? t->alpha_ofs : t->ofs[0] ) : -1;
+		(void)img;
+		it->order0 = order;
+		order += it->count;
+	}
+	RC_CHECK_DEV( rc_dev_set_items( rc.items, rc.nitems, rc.corners, rc.ncorners, rc.sortents, rc.nsortents ));
+}
+
+static void rc_add_studio( cl_entity_t *e )
+{
+	(void)e;
+	if( !rc.warned[5] ) { rc.warned[5] = true; gEngfuncs.Con_Reportf( "ref_cuda: studio models are not drawn yet\n" ); }
+}
+
 static void rc_prepare_batch( void )
 {
 	if( !rc.scene_valid )
@@ -796,6 +1307,7 @@ static void rc_prepare_batch( void )
 	rc_resolve_texnums( false );
 	RC_CHECK_DEV( rc_dev_set_lightstyles( rc.lightstylevalue ));
 	rc_push_dlights();
+	rc_build_items();
 }
 
 static void rc_queue_view( const ref_viewpass_t *rvp )
@@ -988,6 +1500,14 @@ static qboolean R_Init( void )
 	for( int i = 0; i < 1280; i++ ) /* R_InitTurb, ref/soft/r_main.c:1312: AMP + sin( i * 3.14159 * 2 / CYCLE ) * AMP */
 		rc.sintable[i] = ( 8 * 0x10000 ) + sin( i * 3.14159 * 2 / 128 ) * ( 8 * 0x10000 );
 	RC_CHECK_DEV( rc_dev_upload_luts( rc.colormap, rc.lightgamma, rc.sintable ));
+	{
+		uint16_t *alphamap = rc_malloc( sizeof( uint16_t ) * 3 * 1024 * 256 );
+		uint8_t *addmap = rc_malloc( 65536 ), *modmap = rc_malloc( 65536 );
+		rc_build_blendmaps( alphamap, addmap, modmap );
+		RC_CHECK_DEV( rc_dev_upload_blendluts( alphamap, addmap, modmap ));
+		rc_free( alphamap ); rc_free( addmap ); rc_free( modmap );
+	}
+	rc.tri.color = 0xFFFF; rc.tri.alpha = 7; rc.tri.blend = 1.0f;
 
 	if( gpGlobals->width < 128 ) gpGlobals->width = 128;
 	if( gpGlobals->height < 128 ) gpGlobals->height = 128;
@@ -1044,9 +1564,6 @@ static void GL_BackendStartFrame( void ) {}
 static void GL_BackendEndFrame( void ) {}
 static void R_ClearScreen( void ) {}
 static void R_AllowFog( qboolean allow ) { (void)allow; }
-static void GL_SetRenderMode( int renderMode ) { (void)renderMode; }
-static qboolean R_AddEntity( struct cl_entity_s *clent, int type ) { (void)clent; (void)type; return true; }
-static void R_ProcessEntData( qboolean allocate, cl_entity_t *entities, unsigned int max_entities ) { (void)allocate; (void)entities; (void)max_entities; }
 static void R_ShowTextures( void ) {}
 static const byte *R_GetTextureOriginalBuffer( unsigned int idx ) { (void)idx; return NULL; }
 static void GL_ProcessTexture( int texnum, float gamma, int topColor, int bottomColor ) { (void)texnum; (void)gamma; (void)topColor; (void)bottomColor; }
@@ -1110,7 +1627,6 @@ static void R_OverrideTextureSourceSize( unsigned int texnum, unsigned int srcWi
 }
 static void GL_UpdateTexture( int texnum, int cols, int rows, int width, int height, const byte *buffer, pixformat_t fmt )
 { (void)texnum; (void)cols; (void)rows; (void)width; (void)height; (void)buffer; (void)fmt; }
-static void GL_Bind( int tmu, unsigned int texnum ) { (void)tmu; (void)texnum; }
 static void GL_OrthoBounds( const float *mins, const float *maxs ) { (void)mins; (void)maxs; }
 
 static qboolean R_SpeedsMessage( char *out, size_t size )
@@ -1124,15 +1640,6 @@ static qboolean R_SpeedsMessage( char *out, size_t size )
 	return true;
 }
 static byte *Mod_GetCurrentVis( void ) { return NULL; }
-static void R_ClearScene( void ) {}
-static void TriRenderMode( int mode ) { (void)mode; }
-static void TriBegin( int primitiveCode ) { (void)primitiveCode; }
-static void TriEnd( void ) {}
-static void TriColor4f( float r, float g, float b, float a ) { (void)r; (void)g; (void)b; (void)a; }
-static void TriColor4ub( unsigned char r, unsigned char g, unsigned char b, unsigned char a ) { (void)r; (void)g; (void)b; (void)a; }
-static void TriVertex3fv( const float *worldPnt ) { (void)worldPnt; }
-static void TriVertex3f( float x, float y, float z ) { (void)x; (void)y; (void)z; }
-static void TriCullFace( TRICULLSTYLE mode ) { (void)mode; }
 static void R_FillRenderAPI( struct render_api_s *api ) { (void)api; }
 static void R_FillTriAPI( struct triangleapi_s *api ) { (void)api; }
 static void VGUI_SetupDrawing( qboolean rect ) { (void)rect; }

@@ -150,7 +150,57 @@ typedef struct
 	int32_t flags;               /* ref_viewpass_t.flags */
 	float   pvs_radius;
 	int32_t pad[1];
+	float   aliastransform[3][4]; /* R_SetUpWorldTransform (ref/soft/r_trialias.c:52): world -> view space for R_SetupFinalVert */
 } rc_view_t;
+
+/*
+ * Entities (everything that is not a world face goes through the triangle rasteriser, ref/soft/r_polyse.c).  The host
+ * turns the frame's entity lists into an ordered list of draw items - the order R_DrawEntitiesOnList (r_main.c:504)
+ * draws in; translucent entities come with a sort record, their order is per view (R_TransEntityCompare, r_main.c:157).
+ */
+enum { RC_ITEM_TRIS = 0, RC_ITEM_SPRITE = 1, RC_ITEM_MESH = 2 };
+/* the span drawer a texture bind selects (GL_Bind, ref/soft/r_image.c:43-75): R_PolysetFillSpans8, ...Additive, ...Glow,
+ * ...TextureBlended, ...Blended (r_polyse.c:724-1214) */
+enum { RC_DRAW_FILL = 0, RC_DRAW_ADDITIVE = 1, RC_DRAW_GLOW = 2, RC_DRAW_TEXBLEND = 3, RC_DRAW_BLEND = 4 };
+enum { RC_SPR_FWD_PARALLEL_UPRIGHT = 0, RC_SPR_FACING_UPRIGHT = 1, RC_SPR_FWD_PARALLEL = 2, RC_SPR_ORIENTED = 3, RC_SPR_FWD_PARALLEL_ORIENTED = 4 }; /* common/sprite.h */
+
+/* a triangle corner in world space: what TriVertex3f hands to R_SetupFinalVert (r_triapi.c:221) */
+typedef struct
+{
+	float   xyz[3];
+	int32_t l;     /* light << 8 */
+	int16_t s, t;  /* texel, TriTexCoord2f's result */
+} rc_corner_t; /* 20 B */
+
+typedef struct
+{
+	int32_t kind;                 /* RC_ITEM_* */
+	int32_t first, count;         /* TRIS: first corner (3 per triangle) and triangle count; MESH: first static corner, triangle count */
+	int32_t drawer;               /* RC_DRAW_* the texture bind selected (GL_Bind, r_image.c:43) */
+	int32_t tex_ofs, skinwidth, skinheight; /* r_affinetridesc: texel arena offset of pskin, its size */
+	int32_t color, alpha;         /* vid.color, vid.alpha */
+	int32_t sortent;              /* translucent entity the item belongs to (index into the sort records), -1: fixed order */
+	int32_t order0;               /* number of triangles in the items before this one */
+	/* RC_ITEM_SPRITE (R_DrawSpriteModel / R_DrawSpriteQuad, r_sprite.c:120-266) */
+	int32_t sprtype, light;
+	float   origin[3], scale, angles[3];
+	float   fr_up, fr_down, fr_left, fr_right;
+	int16_t s0, s1, t0, t1;       /* texels of texture coordinates 0 and 1 */
+	float   vright[3], vup[3];    /* SPR_ORIENTED: AngleVectors of the entity's angles (origin already pulled back by 0.01 forward) */
+	float   sr, cr;               /* SPR_FWD_PARALLEL_ORIENTED: SinCos of the roll */
+	/* RC_ITEM_MESH: the entity's slices of the batch's transformed vertices and per-normal lights */
+	int32_t vert_base, light_base;
+	int32_t pad[2];
+} rc_item_t; /* 160 B */
+
+/* a translucent entity: R_TransEntityCompare's inputs (r_main.c:157-200) */
+typedef struct
+{
+	float   center[3];    /* origin + average of the model's mins / maxs */
+	int32_t use_dist;     /* 0: distance is 1e9 (a brush model in kRenderTransAlpha) */
+	int32_t rank;         /* R_RankForRenderMode */
+	int32_t pad[3];
+} rc_sortent_t; /* 32 B */
 
 /* a face the BSP walk decided to draw, in front-to-back order (R_RecursiveWorldNode -> R_RenderFace) */
 typedef struct

@@ -91,6 +91,33 @@ class Renderer:
     def run_lightstyles(self):
         self.host.run_lightstyles()
 
+    # -- entities (engine side: the client adds them to the renderer's lists before it asks for views)
+    def create_sprite(self, name, rgba, sprtype=2, texformat=0, texflags=0):
+        """A one-frame sprite model from an RGBA uint8 image [h, w, 4]; sprtype: SPR_* orientation (2 = SPR_FWD_PARALLEL),
+        texformat: 0 normal, 1 additive, 2 indexalpha, 3 alphatest; texflags: TF_* of the frame texture.  -> model index"""
+        rgba = np.ascontiguousarray(rgba, dtype=np.uint8)
+        h, w = rgba.shape[:2]
+        L = self.host.lib
+        L.xh_create_sprite.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int]
+        mi = L.xh_create_sprite(name.encode(), w, h, rgba.ctypes.data, sprtype, texformat, texflags)
+        if mi <= 0:
+            raise RuntimeError("xh_create_sprite failed")
+        return mi
+
+    def add_entity(self, modelindex, origin, angles=(0, 0, 0), rendermode=0, renderamt=255, rendercolor=(0, 0, 0), renderfx=0,
+                   frame=0, sequence=0, body=0, skin=0, scale=1.0, framerate=1.0, animtime=0.0, movetype=0, aiment=0):
+        ip = (C.c_int * 13)(modelindex, rendermode, renderamt, *[int(c) for c in rendercolor], renderfx, frame, sequence, body, skin, movetype, aiment)
+        fp = (C.c_float * 9)(*[float(x) for x in origin], *[float(x) for x in angles], float(scale), float(framerate), float(animtime))
+        L = self.host.lib
+        L.xh_add_entity.argtypes = [C.c_void_p, C.c_void_p]
+        idx = L.xh_add_entity(ip, fp)
+        if idx < 0:
+            raise RuntimeError(f"xh_add_entity failed ({idx})")
+        return idx
+
+    def clear_entities(self):
+        self.host.lib.xh_clear_scene()
+
     # -- views
     def viewpasses(self, cams, fov_x=90.0, flags=RF_DRAW_WORLD, viewport=None):
         cams = np.asarray(cams, dtype=np.float32).reshape(-1, 6)
