@@ -204,8 +204,7 @@ static void emu_draw_items( const rc_view_t *vw, uint16_t *color, int16_t *zb, i
 		if( trans_done ) continue;
 		trans_done = true;
 		for( int e : ents )
-			for( size_t j = 0; j < E.items.size(); j++ )
-				if( E.items[j].sortent == e ) order.push_back( (int)j );
+			for( int j = 0; j < E.sortents[e].nitems; j++ ) order.push_back( E.sortents[e].first_item + j );
 	}
 	for( int idx : order )
 	{

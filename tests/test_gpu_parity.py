@@ -425,3 +425,55 @@ def test_renderer_restart_in_one_process(pkg, scene):
     b, bz = cu.render_views(m.cameras[:4])
     assert np.array_equal(a, b) and np.array_equal(az, bz)
     assert cu.launch_count() > 0
+
+
+# ------------------------------------------------------------------------------------------------
+# entities: the triangle rasteriser
+
+def sprite_image(seed, w=64, h=64):
+    rng = np.random.default_rng(seed)
+    y, x = np.mgrid[0:h, 0:w]
+    d = np.hypot(x - w / 2, y - h / 2) / (w / 2)
+    img = np.zeros((h, w, 4), np.uint8)
+    img[..., 0] = np.clip(255 * (1 - d) + rng.integers(0, 40, (h, w)), 0, 255)
+    img[..., 1] = np.clip(200 * (1 - d * d), 0, 255)
+    img[..., 2] = rng.integers(0, 255, (h, w))
+    img[..., 3] = np.where(d < 0.9, 255, 0)
+    return img
+
+
+def add_test_sprites(r, m, spots, sprtypes=(2,)):
+    """sprites of every span drawer next to the given cameras: kRenderNormal (R_PolysetFillSpans8), kRenderTransAdd
+    (...Additive), kRenderTransAlpha on an alpha texture (...TextureBlended), kRenderTransTexture (...Blended)"""
+    TF_HAS_ALPHA = 1 << 20
+    mods = {}
+    for st in sprtypes:
+        mods[st] = [r.create_sprite(f"spr_add{st}", sprite_image(1), sprtype=st, texformat=1),
+                    r.create_sprite(f"spr_norm{st}", sprite_image(2, 32, 48), sprtype=st, texformat=0),
+                    r.create_sprite(f"spr_alpha{st}", sprite_image(3), sprtype=st, texformat=3, texflags=TF_HAS_ALPHA)]
+    for k, c in enumerate(spots):
+        st = sprtypes[k % len(sprtypes)]
+        r.add_entity(mods[st][[0, 1, 2, 0][k % 4]], c[:3], angles=(0.0, 30.0 * k, 20.0 * (k % 3)),
+                     rendermode=[5, 0, 4, 2][k % 4], renderamt=[255, 255, 255, 128][k % 4],
+                     rendercolor=[(0, 0, 0), (255, 255, 255), (255, 128, 64), (10, 200, 255)][k % 4], scale=[1.0, 0.5, 1.0, 2.0][k % 4])
+
+
+@pytest.mark.parametrize("sprtypes", [(2,), (0, 1, 3, 4)])
+def test_sprites_match_oracle(pkg, scene, sprtypes):
+    """R_DrawSpriteModel / R_DrawSpriteQuad / TriAPI / R_AliasClipTriangle / R_DrawTriangle and four of the five span
+    drawers: 32 sprites (all orientation types) in 32 views, sorted per view like R_TransEntityCompare does."""
+    m = scene.make_map("small", ncameras=64)
+    cu = scene.Renderer(pkg.REF_CUDA_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    bare, _ = so.render_views(m.cameras[:32])
+    for r in (cu, so):
+        add_test_sprites(r, m, m.cameras[32:64], sprtypes)
+    cc, cz = cu.render_views(m.cameras[:32])
+    rc, rz = so.render_views(m.cameras[:32])
+    assert (rc != bare).mean() > 0.02, "the oracle drew no sprites"
+    assert np.array_equal(cc, rc) and np.array_equal(cz, rz), ((cc == rc).mean(), (cz == rz).mean())
+    assert cu.counters()["tris"] > 0
+    for r in (cu, so):
+        r.clear_entities()
+    cc, _ = cu.render_views(m.cameras[:32])
+    assert np.array_equal(cc, bare)  # R_ClearScene empties the lists

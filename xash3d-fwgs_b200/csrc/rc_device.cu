@@ -82,6 +82,12 @@ struct rc_work_t
 	uint16_t  *color;
 	int16_t   *zbuf;
 	unsigned long long *counters;
+	/* entities (rc_k_tris.cuh) */
+	const rc_item_t *items; const rc_corner_t *corners; const rc_sortent_t *sortents;
+	int32_t    nitems, nsortents;
+	int32_t   *item_order;  /* [nviews][nitems] */
+	struct rc_poly_t *polys; /* [nviews][ntris] */
+	const uint16_t *alphamap; const uint8_t *addmap, *modmap;
 };
 
 #define SP_LINES 32 /* scanlines per band (rc_k_spans.cuh): k_faces bins edges by band */
@@ -436,6 +442,7 @@ __global__ void __launch_bounds__( CACHE_THREADS ) k_cache_build( rc_scene_t sc,
 
 #include "rc_k_spans.cuh"
 #include "rc_k_draw.cuh"
+#include "rc_k_tris.cuh"
 
 /* ---------------------------------------------------------------------------------------------- */
 /* host side of the C layer                                                                          */
@@ -598,6 +605,9 @@ struct Dev
 	rc_item_t *d_items = nullptr; rc_corner_t *d_corners = nullptr; rc_sortent_t *d_sortents = nullptr;
 	int nitems = 0, ncorners = 0, nsortents = 0;
 	std::vector<rc_item_t> h_items;
+	int ntris = 0;                       /* triangles of the items */
+	int32_t *d_item_order = nullptr; rc_poly_t *d_polys = nullptr;
+	size_t cap_item_order = 0, cap_polys = 0;
 
 	/* dynamic lights of the next batch */
 	rc_dlight_t *d_dlights = nullptr;
@@ -810,6 +820,10 @@ rc_work_t make_slice( int k, int v0, int v1 )
 	ws.wide_list += (size_t)v0 * ws.height;
 	ws.styles = D.d_styles; ws.counters = D.d_counters;
 	ws.dlights = D.d_dlights; ws.dlightbits = D.d_dlightbits; ws.ndlights = D.ndlights;
+	ws.items = D.d_items; ws.corners = D.d_corners; ws.sortents = D.d_sortents; ws.nitems = D.nitems; ws.nsortents = D.nsortents;
+	ws.item_order = D.d_item_order ? D.d_item_order + (size_t)v0 * D.nitems : nullptr;
+	ws.polys = D.d_polys ? D.d_polys + (size_t)v0 * D.ntris : nullptr;
+	ws.alphamap = D.d_alphamap; ws.addmap = D.d_addmap; ws.modmap = D.d_modmap;
 	return ws;
 }
 
@@ -867,6 +881,16 @@ int launch_slice( const rc_work_t &ws, int k, cudaStream_t st, cudaEvent_t *evs,
 		k_draw<<<dblocks < DR_GRID ? dblocks : DR_GRID, DR_WARPS * 32, rc_draw_smem( ws.width, lpw ), st>>>( sc, ws, 0, nlines, lpw );
 		D.launches++;
 		KCHECK( "k_draw", st );
+		if( D.nitems && D.ntris )
+		{
+			/* entities: after the world's spans are in the frame (R_DrawEntitiesOnList follows R_EdgeDrawing, r_main.c:1090) */
+			k_item_order<<<ws.nviews, 128, 0, st>>>( ws ); D.launches++;
+			dim3 gp(( D.ntris + 127 ) / 128, ws.nviews );
+			k_tri_polys<<<gp, 128, 0, st>>>( ws, D.ntris ); D.launches++;
+			dim3 gt( ws.nviews, TR_STRIPS );
+			k_tris_ordered<<<gt, TR_THREADS, 0, st>>>( sc, ws, D.ntris ); D.launches++;
+			KCHECK( "k_tris", st );
+		}
 	}
 	if( evs ) CK( cudaEventRecord( evs[5], st ));
 	return 0;
@@ -964,7 +988,7 @@ void rc_dev_shutdown( void )
 	cudaDeviceSynchronize();
 	free_batch();
 	/* everything rc_dev_init / the uploads created, so that R_Shutdown + R_Init (vid_restart) starts clean */
-	void **ptrs[] = { (void **)&D.d_alphamap, (void **)&D.d_addmap, (void **)&D.d_modmap, (void **)&D.d_items, (void **)&D.d_corners, (void **)&D.d_sortents, (void **)&D.d_display, (void **)&D.d_screenmap, (void **)&D.d_dlights, (void **)&D.d_dlightbits,
+	void **ptrs[] = { (void **)&D.d_item_order, (void **)&D.d_polys, (void **)&D.d_alphamap, (void **)&D.d_addmap, (void **)&D.d_modmap, (void **)&D.d_items, (void **)&D.d_corners, (void **)&D.d_sortents, (void **)&D.d_display, (void **)&D.d_screenmap, (void **)&D.d_dlights, (void **)&D.d_dlightbits,
 		(void **)&D.d_colormap, (void **)&D.d_lightgamma, (void **)&D.d_sintable, (void **)&D.d_textures, (void **)&D.d_texels,
 		(void **)&D.d_styles, (void **)&D.d_keys, (void **)&D.d_need, (void **)&D.d_list, (void **)&D.d_nlist,
 		(void **)&D.d_counters, &D.d_flush };
@@ -972,7 +996,7 @@ void rc_dev_shutdown( void )
 	for( void *&p : D.d_scene ) { if( p ) cudaFree( p ); p = nullptr; }
 	if( D.h_counters ) { cudaFreeHost( D.h_counters ); D.h_counters = nullptr; }
 	D.cap_cands = D.cap_edges = D.cap_blk_events = 0; D.caps_dirty = false;
-	D.nitems = D.ncorners = D.nsortents = 0; D.h_items.clear();
+	D.nitems = D.ncorners = D.nsortents = 0; D.h_items.clear(); D.ntris = 0; D.cap_item_order = D.cap_polys = 0;
 	D.display_bytes = 0; D.ndlights = 0; D.screen_bpp = 0; D.cache_texels = 0; D.ntextures = 0;
 	D.sc = rc_scene_t{}; D.h_surfaces.clear(); D.h_textures.clear();
 	cudaStream_t *streams[] = { &D.stream, &D.copy };
@@ -1117,11 +1141,13 @@ int rc_dev_set_items( const rc_item_t *items, int nitems, const rc_corner_t *cor
 	if( !nitems && !D.nitems ) return 0;
 	CK( cudaStreamSynchronize( D.stream ));
 	D.nitems = nitems; D.nsortents = nsortents; D.ncorners = ncorners;
-	if( !nitems ) return 0;
+	if( !nitems ) { D.ntris = 0; return 0; }
 	if( upload( &D.d_items, items, (size_t)nitems ) != 0 ) return -1;
 	if( upload( &D.d_corners, corners, (size_t)ncorners ) != 0 ) return -1;
 	if( upload( &D.d_sortents, sortents, (size_t)nsortents ) != 0 ) return -1;
 	D.h_items.assign( items, items + nitems );
+	D.ntris = 0;
+	for( int i = 0; i < nitems; i++ ) D.ntris += items[i].count;
 	D.h2d_bytes += sizeof( rc_item_t ) * (size_t)nitems + sizeof( rc_corner_t ) * (size_t)ncorners + sizeof( rc_sortent_t ) * (size_t)nsortents;
 	return 0;
 }
@@ -1184,6 +1210,12 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 	for( int attempt = 0; ; attempt++ )
 	{
 		if( ensure_batch( nviews, width, height ) != 0 ) return -1;
+		if( D.nitems && D.ntris )
+		{
+			const size_t need_o = (size_t)D.cap_views * D.nitems, need_p = (size_t)D.cap_views * D.ntris;
+			if( need_o > D.cap_item_order ) { if( dalloc( &D.d_item_order, need_o ) != 0 ) return -1; D.cap_item_order = need_o; }
+			if( need_p > D.cap_polys ) { if( dalloc( &D.d_polys, need_p ) != 0 ) return -1; D.cap_polys = need_p; }
+		}
 		rc_work_t &w = D.w;
 		w.nviews = nviews; w.clear = clear;
 		cudaStream_t st = D.stream;

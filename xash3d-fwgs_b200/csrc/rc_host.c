@@ -1260,6 +1260,7 @@ static void rc_build_items( void )
 		VectorAdd( e->origin, org, se->center );
 		se->use_dist = ( e->model->type != mod_brush || rendermode != kRenderTransAlpha ) ? 1 : 0;
 		se->rank = rendermode == kRenderTransTexture ? 1 : rendermode == kRenderTransAdd ? 2 : rendermode == kRenderGlow ? 3 : 0;
+		se->first_item = rc.nitems;
 		rc.cur_sortent = rc.nsortents++;
 		switch( e->model->type )
 		{
@@ -1270,6 +1271,7 @@ static void rc_build_items( void )
 			break;
 		default: break;
 		}
+		rc.sortents[rc.cur_sortent].nitems = rc.nitems - rc.sortents[rc.cur_sortent].first_item;
 	}
 	rc.cur_sortent = -1;
 	rc.tri.blend = 1.0f;

@@ -1,0 +1,200 @@
+/*
+ * rc_k_tris.cuh - S5, entities: everything ref_soft draws that is not a world face goes through its triangle
+ * rasteriser (R_DrawEntitiesOnList -> TriAPI -> R_RenderTriangle -> R_DrawTriangle, ref/soft/r_main.c:504,
+ * r_triapi.c:221, r_trialias.c:171, r_polyse.c:636), after the world's spans are in the frame.  The arithmetic is
+ * rc_tri.h; here is the decomposition:
+ *
+ *   k_item_order  block per view: the order the view's draw items are drawn in - the fixed ones as the host listed them,
+ *                 the translucent entities sorted far to near by R_TransEntityCompare (r_main.c:157) for THIS eye.
+ *   k_tri_polys   thread per (view, triangle): world-space corners (recorded TriAPI corners, or a sprite's quad built
+ *                 from the view's axes, r_sprite.c:120-266) -> R_SetupFinalVert, trivial reject, R_AliasClipTriangle ->
+ *                 the screen-space polygon the reference would fan into triangles, left in HBM.
+ *   k_tris_ordered  the span drawers read and write the frame, and all but the opaque one blend: triangles have to
+ *                 reach a pixel in submission order.  Block per (view, horizontal strip of the frame): it walks the
+ *                 view's triangles in order; per triangle one thread sets up the edge walk (rc_tri_setup), then the
+ *                 block's warps take the scanlines inside the strip, lanes the pixels of a scanline - every scanline and
+ *                 pixel is closed form (rc_tri_row), so the result is the reference's sequential one.
+ */
+#ifndef RC_K_TRIS_CUH
+#define RC_K_TRIS_CUH
+
+#include "rc_tri.h"
+
+#define TR_THREADS 128
+#define TR_STRIPS  4     /* horizontal strips of a frame drawn by different blocks */
+
+struct rc_poly_t
+{
+	int32_t k;           /* vertices, 0 = nothing to draw */
+	int32_t v[8][6];     /* u, v, s, t, l, zi */
+}; /* 196 B */
+
+/* the order the items of one view are drawn in */
+__global__ void __launch_bounds__( 128 ) k_item_order( rc_work_t w )
+{
+	const int view = blockIdx.x, t = threadIdx.x;
+	const rc_view_t *vw = &w.views[view];
+	int32_t *order = w.item_order + (size_t)view * w.nitems;
+	__shared__ int32_t s_pos[2048]; /* MAX_VISIBLE_PACKET translucent entities: position of entity e in the sorted list */
+	const int32_t ns = w.nsortents < 2048 ? w.nsortents : 2048;
+	for( int32_t a = t; a < ns; a += blockDim.x )
+	{
+		const rc_sortent_t sa = w.sortents[a];
+		float v[3] = { vw->origin[0] - sa.center[0], vw->origin[1] - sa.center[1], vw->origin[2] - sa.center[2] };
+		const float da = sa.use_dist ? rc_dot3( v, v ) : 1000000000.0f;
+		int32_t before = 0;
+		for( int32_t b = 0; b < ns; b++ )
+		{
+			const rc_sortent_t sb = w.sortents[b];
+			float u[3] = { vw->origin[0] - sb.center[0], vw->origin[1] - sb.center[1], vw->origin[2] - sb.center[2] };
+			const float db = sb.use_dist ? rc_dot3( u, u ) : 1000000000.0f;
+			/* farther first, then the lower render-mode rank; equal keys keep the list order (merge sort is stable) */
+			if( db > da || ( db == da && ( sb.rank < sa.rank || ( sb.rank == sa.rank && b < a )))) before++;
+		}
+		s_pos[before] = a;
+	}
+	__syncthreads();
+	if( t == 0 )
+	{
+		int32_t n = 0;
+		bool trans_done = false;
+		for( int32_t i = 0; i < w.nitems; i++ )
+		{
+			if( w.items[i].sortent < 0 ) { order[n++] = i; continue; }
+			if( trans_done ) continue;
+			trans_done = true;
+			for( int32_t p = 0; p < ns; p++ )
+			{
+				const rc_sortent_t se = w.sortents[s_pos[p]];
+				for( int32_t j = 0; j < se.nitems; j++ ) order[n++] = se.first_item + j;
+			}
+		}
+		for( ; n < w.nitems; n++ ) order[n] = -1;
+	}
+}
+
+/* world-space corners of triangle tri of an item for a view; 0 = not drawn */
+__device__ __forceinline__ int rc_item_corners( const rc_work_t &w, const rc_view_t *vw, const rc_item_t *it, int32_t tri, rc_corner_t *c )
+{
+	if( it->kind == RC_ITEM_SPRITE )
+	{
+		rc_corner_t q[4];
+		if( !rc_sprite_corners( vw, it, q ))
+			return 0;
+		c[0] = q[0];
+		c[1] = tri ? q[2] : q[1];
+		c[2] = tri ? q[3] : q[2];
+		return 1;
+	}
+	const rc_corner_t *src = w.corners + it->first + 3 * tri;
+	c[0] = src[0]; c[1] = src[1]; c[2] = src[2];
+	return 1;
+}
+
+__global__ void __launch_bounds__( 128 ) k_tri_polys( rc_work_t w, int32_t ntris )
+{
+	const int view = blockIdx.y;
+	const int32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+	if( g >= ntris )
+		return;
+	/* the item this triangle belongs to: items are few, their order0 ascending */
+	int32_t lo = 0, hi = w.nitems - 1;
+	while( lo < hi )
+	{
+		const int32_t mid = ( lo + hi + 1 ) >> 1;
+		if( w.items[mid].order0 <= g ) lo = mid; else hi = mid - 1;
+	}
+	const rc_item_t *it = &w.items[lo];
+	const rc_view_t *vw = &w.views[view];
+	rc_poly_t *out = w.polys + (size_t)view * ntris + g;
+	rc_corner_t c[3];
+	rc_fv_t poly[8];
+	int k = 0;
+	if( it->tex_ofs >= 0 && g - it->order0 < it->count && rc_item_corners( w, vw, it, g - it->order0, c ))
+		k = rc_view_triangle( vw, &c[0], &c[1], &c[2], poly );
+	out->k = k;
+	for( int i = 0; i < k; i++ )
+	{
+		out->v[i][0] = poly[i].u; out->v[i][1] = poly[i].v; out->v[i][2] = poly[i].s;
+		out->v[i][3] = poly[i].t; out->v[i][4] = poly[i].l; out->v[i][5] = poly[i].zi;
+	}
+}
+
+__global__ void __launch_bounds__( TR_THREADS ) k_tris_ordered( rc_scene_t sc, rc_work_t w, int32_t ntris )
+{
+	__shared__ rc_trisetup_t s_ts;
+	__shared__ int32_t s_go, s_y0, s_rows;
+	const int view = blockIdx.x, strip = blockIdx.y, t = threadIdx.x, lane = t & 31, warp = t >> 5;
+	const int32_t ys0 = (int32_t)((long long)w.height * strip / gridDim.y ), ys1 = (int32_t)((long long)w.height * ( strip + 1 ) / gridDim.y );
+	uint16_t *color = w.color + (size_t)view * w.width * w.height;
+	int16_t *zb = w.zbuf + (size_t)view * w.width * w.height;
+	const int32_t *order = w.item_order + (size_t)view * w.nitems;
+	const rc_poly_t *polys = w.polys + (size_t)view * ntris;
+	rc_blendluts_t L;
+	L.colormap = sc.colormap; L.alphamap = w.alphamap; L.addmap = w.addmap; L.modmap = w.modmap;
+	unsigned long long npix = 0, ndrawn = 0;
+
+	for( int32_t oi = 0; oi < w.nitems; oi++ )
+	{
+		const int32_t idx = order[oi];
+		if( idx < 0 )
+			break;
+		const rc_item_t *it = &w.items[idx];
+		if( it->tex_ofs < 0 )
+			continue;
+		const uint16_t *skin = sc.texels + it->tex_ofs;
+		const int32_t drawer = it->drawer;
+		const uint32_t icolor = (uint32_t)it->color, ialpha = (uint32_t)it->alpha;
+		for( int32_t tri = 0; tri < it->count; tri++ )
+		{
+			const rc_poly_t *pl = &polys[it->order0 + tri];
+			const int32_t k = pl->k;
+			for( int32_t i = 1; i < k - 1; i++ )
+			{
+				__syncthreads(); /* the previous triangle's pixels are in the frame; s_ts is free */
+				if( t == 0 )
+				{
+					rc_fv_t a, b, c;
+					const int32_t *pa = pl->v[0], *pb = pl->v[i], *pc = pl->v[i + 1];
+					a.u = pa[0]; a.v = pa[1]; a.s = pa[2]; a.t = pa[3]; a.l = pa[4]; a.zi = pa[5];
+					b.u = pb[0]; b.v = pb[1]; b.s = pb[2]; b.t = pb[3]; b.l = pb[4]; b.zi = pb[5];
+					c.u = pc[0]; c.v = pc[1]; c.s = pc[2]; c.t = pc[3]; c.l = pc[4]; c.zi = pc[5];
+					int go = rc_tri_setup( &a, &b, &c, it->skinwidth, it->skinheight, &s_ts );
+					int32_t y0 = 0, rows = 0;
+					if( go )
+					{
+						rows = rc_tri_rows( &s_ts, &y0 );
+						if( strip == 0 ) ndrawn++;
+						go = y0 < ys1 && y0 + rows > ys0;
+					}
+					s_go = go; s_y0 = y0; s_rows = rows;
+				}
+				__syncthreads();
+				if( !s_go )
+					continue;
+				const int32_t y0 = s_y0;
+				const int32_t rlo = ys0 > y0 ? ys0 - y0 : 0, rhi = min( s_rows, ys1 - y0 );
+				for( int32_t r = rlo + warp; r < rhi; r += TR_THREADS / 32 )
+				{
+					rc_trirow_t row;
+					rc_tri_row( &s_ts, r, &row );
+					if( row.count <= 0 || !rc_tri_row_inbounds( &s_ts, &row ))
+						continue;
+					const size_t base = (size_t)( y0 + r ) * w.width + row.x;
+					for( int32_t p = lane; p < row.count; p += 32 )
+					{
+						const uint32_t src = __ldg( skin + rc_tri_texel( &s_ts, &row, p ));
+						const int32_t light = (int32_t)((uint32_t)row.l + (uint32_t)p * (uint32_t)s_ts.lstepx );
+						const int32_t zi = (int32_t)((uint32_t)row.zi + (uint32_t)p * (uint32_t)s_ts.zistepx );
+						rc_tri_shade( &L, drawer, icolor, ialpha, src, light, zi, &color[base + p], &zb[base + p] );
+					}
+					if( lane == 0 ) npix += (unsigned long long)row.count;
+				}
+			}
+		}
+	}
+	if( lane == 0 && npix ) atomicAdd( &w.counters[RC_CTR_TRI_PIXELS], npix );
+	if( t == 0 && ndrawn ) atomicAdd( &w.counters[RC_CTR_TRIS], ndrawn );
+}
+
+#endif /* RC_K_TRIS_CUH */

@@ -199,7 +199,8 @@ typedef struct
 	float   center[3];    /* origin + average of the model's mins / maxs */
 	int32_t use_dist;     /* 0: distance is 1e9 (a brush model in kRenderTransAlpha) */
 	int32_t rank;         /* R_RankForRenderMode */
-	int32_t pad[3];
+	int32_t first_item, nitems; /* the entity's draw items (contiguous in the list) */
+	int32_t pad[1];
 } rc_sortent_t; /* 32 B */
 
 /* a face the BSP walk decided to draw, in front-to-back order (R_RecursiveWorldNode -> R_RenderFace) */
