@@ -29,6 +29,7 @@ struct Emu
 	std::vector<int32_t> sintable, sedgepartner; std::vector<float> sedgeverts;
 	std::vector<uint16_t> alphamap; std::vector<uint8_t> addmap, modmap;
 	std::vector<rc_item_t> items; std::vector<rc_corner_t> corners; std::vector<rc_sortent_t> sortents;
+	std::vector<uint8_t> sstatic; std::vector<rc_spart_t> parts; std::vector<float> bones, blight, mvpos; std::vector<int32_t> mlight;
 	int32_t styles[256];
 	struct Key { int32_t texnum; int32_t light[4]; bool valid; };
 	std::vector<Key> cachekey;
@@ -147,6 +148,30 @@ int rc_dev_set_items( const rc_item_t *items, int nitems, const rc_corner_t *cor
 	return 0;
 }
 
+int rc_dev_upload_studio_static( const void *arena, size_t bytes )
+{
+	E.sstatic.assign( (const uint8_t *)arena, (const uint8_t *)arena + bytes );
+	return 0;
+}
+
+/* the batch's studio parts: vertices through their bones, one light level per normal (k_studio_points on the device) */
+int rc_dev_set_studio( const rc_spart_t *parts, int nparts, const float *bones, int nbones, const float *blightvecs, int totalverts, int totalnorms )
+{
+	E.parts.assign( parts, parts + nparts );
+	E.bones.assign( bones, bones + (size_t)nbones * 12 ); E.blight.assign( blightvecs, blightvecs + (size_t)nbones * 3 );
+	E.mvpos.assign( (size_t)totalverts * 3 + 3, 0.0f ); E.mlight.assign( (size_t)totalnorms + 1, 0 );
+	const float *sf = (const float *)E.sstatic.data();
+	for( const rc_spart_t &pt : E.parts )
+	{
+		for( int i = 0; i < pt.numverts; i++ )
+			rc_studio_vertex( &E.bones[(size_t)( pt.bones + E.sstatic[pt.svertbone + i] ) * 12], sf + pt.sverts + 3 * i, &E.mvpos[(size_t)( pt.vert_base + i ) * 3] );
+		for( int k = 0; k < pt.numnorms; k++ )
+			E.mlight[pt.light_base + k] = rc_studio_light( &pt, E.sstatic[pt.snormflags + k], sf + pt.snorms + 3 * k,
+				&E.blight[(size_t)( pt.blightvec + E.sstatic[pt.snormbone + k] ) * 3], E.lightgamma.data());
+	}
+	return 0;
+}
+
 /* one polygon fan of the triangle rasteriser, scanline by scanline (what the kernels do per row / per pixel) */
 static void emu_draw_poly( const rc_item_t *it, const rc_fv_t *poly, int k, uint16_t *color, int16_t *zb, int width )
 {
@@ -219,6 +244,23 @@ static void emu_draw_items( const rc_view_t *vw, uint16_t *color, int16_t *zb, i
 			if( k ) emu_draw_poly( it, poly, k, color, zb, width );
 			k = rc_view_triangle( vw, &q[0], &q[2], &q[3], poly );
 			if( k ) emu_draw_poly( it, poly, k, color, zb, width );
+		}
+		else if( it->kind == RC_ITEM_MESH )
+		{
+			const rc_mcorner_t *mc = (const rc_mcorner_t *)E.sstatic.data() + it->first;
+			for( int t = 0; t < it->count; t++ )
+			{
+				rc_corner_t c[3];
+				for( int q = 0; q < 3; q++ )
+				{
+					const rc_mcorner_t &m = mc[3 * t + q];
+					const float *p = &E.mvpos[(size_t)( it->vert_base + m.vert ) * 3];
+					c[q].xyz[0] = p[0]; c[q].xyz[1] = p[1]; c[q].xyz[2] = p[2];
+					c[q].l = E.mlight[it->light_base + m.norm]; c[q].s = m.s; c[q].t = m.t;
+				}
+				int k = rc_view_triangle( vw, &c[0], &c[1], &c[2], poly );
+				if( k ) emu_draw_poly( it, poly, k, color, zb, width );
+			}
 		}
 		else if( it->kind == RC_ITEM_TRIS )
 		{

@@ -17,6 +17,8 @@
 #include "xh_internal.h"
 #include "pm_defs.h"
 #include "sprite.h"
+#include "studio.h"
+#include "r_studioint.h"
 
 xh_state_t xh;
 
@@ -265,7 +267,8 @@ static double xh_Time( void ) { return xh.host.realtime; }
 static void xh_Image_SetForceFlags( uint f ) { (void)f; }
 static void xh_Image_ClearForceFlags( void ) {}
 static qboolean xh_Image_CustomPalette( void ) { return false; }
-static void xh_Image_SetMDLPointer( byte *p ) { (void)p; }
+byte *xh_mdl_pointer;
+static void xh_Image_SetMDLPointer( byte *p ) { xh_mdl_pointer = p; }
 static qboolean xh_Image_Process( rgbdata_t **pix, int w, int h, uint flags, float r ) { (void)pix; (void)w; (void)h; (void)flags; (void)r; return true; }
 
 /* world as physent 0 (pmove->physents[0], engine/client/cl_pmove.c): light tracing walks it */
@@ -305,6 +308,7 @@ static intptr_t (*const xh_stubs[XH_NSTUBS])( void ) = {
 };
 
 static mspriteframe_t *xh_R_GetSpriteFrame( const model_t *pModel, int frame, float yaw );
+static void *xh_R_StudioGetAnim( studiohdr_t *hdr, model_t *mod, mstudioseqdesc_t *pseqdesc );
 
 static void xh_fill_engfuncs( ref_api_t *e )
 {
@@ -374,11 +378,13 @@ static void xh_fill_engfuncs( ref_api_t *e )
 	e->EV_GetPhysent = xh_EV_GetPhysent;
 	e->SetLocalLightLevel = xh_SetLocalLightLevel;
 	e->CL_GetRemapInfoForEntity = (void *)xh_null_ptr;
+	e->CL_EntitySetRemapColors = (void *)xh_null_ptr; /* no colour remapping in the harness: returns false */
+	e->pfnStudioEvent = (void *)xh_null_ptr;
 	e->pfnPlayerInfo = (void *)xh_null_ptr;
 	e->pfnGetPlayerState = (void *)xh_null_ptr;
 	e->GetDefaultSprite = (void *)xh_null_ptr;
 	e->R_GetSpriteFrame = (void *)xh_R_GetSpriteFrame;
-	e->R_StudioGetAnim = (void *)xh_null_ptr;
+	e->R_StudioGetAnim = (void *)xh_R_StudioGetAnim;
 	e->CL_AllocElight = (void *)xh_null_ptr;
 	e->EV_TraceSurface = (void *)xh_null_ptr;
 	e->GetScreenFade = (void *)xh_null_ptr;
@@ -438,8 +444,22 @@ static void xh_builtin_textures( void )
 
 /* ------------------------------------------------------------------ */
 
+#include <execinfo.h>
+#include <signal.h>
+#include <unistd.h>
+/* XH_BACKTRACE in the environment: a fault inside a renderer prints its frames (no debugger on the boxes) */
+static void xh_on_fault( int sig )
+{
+	void *frames[48];
+	int n = backtrace( frames, 48 );
+	dprintf( 2, "[xh_host] signal %d\n", sig );
+	backtrace_symbols_fd( frames, n, 2 );
+	_exit( 128 + sig );
+}
+
 int xh_init( const char *ref_path, int width, int height )
 {
+	if( getenv( "XH_BACKTRACE" )) { signal( SIGSEGV, xh_on_fault ); signal( SIGBUS, xh_on_fault ); signal( SIGFPE, xh_on_fault ); }
 	if( xh.dll ) { snprintf( xh_errbuf, sizeof( xh_errbuf ), "already initialised" ); return -1; }
 
 	xh.verbose = getenv( "XH_VERBOSE" ) != NULL;
@@ -480,6 +500,14 @@ int xh_init( const char *ref_path, int width, int height )
 	}
 	xh_builtin_textures();
 	xh.ref.R_ProcessEntData( true, xh.entities, xh.max_entities );
+	/* CL_InitStudioAPI (engine/client/dll_int/cl_game.c:3966): no client DLL overrides the studio interface here, the
+	 * renderer's default one is installed */
+	{
+		static engine_studio_api_t studio_api;
+		static r_studio_interface_t default_draw;
+		if( xh.ref.R_StudioFillAPI( &studio_api, &default_draw ))
+			xh.ref.R_StudioSetDrawInterface( &default_draw );
+	}
 	return 0;
 }
 
@@ -603,6 +631,35 @@ static model_t *xh_new_model( const char *name, modtype_t type )
 	m->needload = 1; /* NL_PRESENT */
 	xh.cl.models[++xh.cl.nummodels] = m;
 	return m;
+}
+
+/* engine/common/mod_studio.c R_StudioGetAnim: sequence group 0 lives in the model file itself (demand-loaded groups
+ * are not part of this harness) */
+static void *xh_R_StudioGetAnim( studiohdr_t *hdr, model_t *mod, mstudioseqdesc_t *pseqdesc )
+{
+	(void)mod;
+	if( !hdr || !pseqdesc || pseqdesc->seqgroup != 0 ) return NULL;
+	return (byte *)hdr + pseqdesc->animindex;
+}
+
+/* a studio model from an MDL v10 image in memory: what Mod_LoadStudioModel (engine/common/mod_studio.c:1126) leaves in
+ * model_t - a private copy of the file as cache.data, textures handed to the renderer, bounds from the header */
+int xh_load_studio( const char *name, const void *buffer, size_t len )
+{
+	const studiohdr_t *in = (const studiohdr_t *)buffer;
+	if( !buffer || len < sizeof( studiohdr_t ) || in->ident != IDSTUDIOHEADER || in->version != STUDIO_VERSION || (size_t)in->length > len )
+		return -1;
+	model_t *m = xh_new_model( name, mod_studio );
+	if( !m ) return -1;
+	m->cache.data = malloc( in->length );
+	memcpy( m->cache.data, buffer, in->length );
+	studiohdr_t *phdr = (studiohdr_t *)m->cache.data;
+	xh.ref.Mod_StudioLoadTextures( m, phdr );
+	for( int i = 0; i < 3; i++ ) { m->mins[i] = phdr->bbmin[i]; m->maxs[i] = phdr->bbmax[i]; }
+	m->numframes = 1;
+	m->flags = phdr->flags;
+	xh.ref.Mod_ProcessRenderData( m, true, buffer, len );
+	return xh.cl.nummodels;
 }
 
 /* a one-frame sprite model from an RGBA image: what Mod_LoadSpriteModel leaves in model_t (msprite_t with SPR_SINGLE

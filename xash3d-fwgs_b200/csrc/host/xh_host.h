@@ -56,6 +56,8 @@ XH_EXPORT int xh_add_brush_entity( int modelindex, const float *origin, const fl
 /* a one-frame sprite model from an RGBA image (type: SPR_* orientation, texformat: SPR_NORMAL / ADDITIVE / INDEXALPHA /
  * ALPHTEST, texflags: TF_* for the frame's texture); returns the model index */
 XH_EXPORT int xh_create_sprite( const char *name, int w, int h, const void *rgba, int type, int texformat, int texflags );
+/* a studio model from an MDL v10 file image; returns the model index */
+XH_EXPORT int xh_load_studio( const char *name, const void *buffer, size_t len );
 /* any model as an entity of the next views; ip[13]: modelindex, rendermode, renderamt, r, g, b, renderfx, frame, sequence,
  * body, skin, movetype, aiment; fp[9]: origin, angles, scale, framerate, animtime.  Returns the entity index */
 XH_EXPORT int xh_add_entity( const int *ip, const float *fp );

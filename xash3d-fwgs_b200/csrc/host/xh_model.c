@@ -14,6 +14,7 @@
 #include <string.h>
 
 #include "xh_internal.h"
+#include "studio.h"
 #include "wadfile.h"
 
 /* ------------------------------------------------------------------ */
@@ -69,9 +70,38 @@ const void *xh_gamma_table( int which, int *count )
 /* images: FS_LoadImage for "#map:name.mip" buffers (engine/common/imagelib/img_wad.c Image_LoadMIP) */
 /* 8-bit indexed miptex + 256-entry palette after the 4th mip -> RGBA8    */
 
+extern byte *xh_mdl_pointer;
+
+/* engine/common/imagelib/img_wad.c Image_LoadMDL: a studio model skin - mstudiotexture_t header, 8-bit indices at the
+ * pointer the renderer announced through Image_SetMDLPointer, the palette right after them */
+static rgbdata_t *xh_load_mdl_skin( const byte *buffer )
+{
+	const mstudiotexture_t *tx = (const mstudiotexture_t *)buffer;
+	const byte *src = xh_mdl_pointer;
+	if( !src || tx->width <= 0 || tx->height <= 0 || tx->width > 4096 || tx->height > 4096 ) return NULL;
+	const size_t pixels = (size_t)tx->width * tx->height;
+	const byte *pal = src + pixels;
+	rgbdata_t *pic = calloc( 1, sizeof( *pic ));
+	pic->width = tx->width; pic->height = tx->height; pic->depth = 1;
+	pic->type = PF_RGBA_32; pic->flags = IMAGE_HAS_COLOR; pic->size = pixels * 4; pic->numMips = 1;
+	pic->buffer = malloc( pic->size );
+	const qboolean masked = FBitSet( tx->flags, STUDIO_NF_MASKED );
+	for( size_t i = 0; i < pixels; i++ )
+	{
+		const byte idx = src[i];
+		byte *out = pic->buffer + i * 4;
+		if( masked && idx == 255 ) { out[0] = out[1] = out[2] = out[3] = 0; pic->flags |= IMAGE_HAS_ALPHA | IMAGE_ONEBIT_ALPHA; }
+		else { out[0] = pal[idx * 3]; out[1] = pal[idx * 3 + 1]; out[2] = pal[idx * 3 + 2]; out[3] = 255; }
+	}
+	return pic;
+}
+
 rgbdata_t *xh_FS_LoadImage( const char *filename, const byte *buffer, size_t size )
 {
 	xh.callbacks++;
+	const size_t fl = filename ? strlen( filename ) : 0;
+	if( buffer && fl > 4 && !strcmp( filename + fl - 4, ".mdl" ))
+		return xh_load_mdl_skin( buffer );
 	if( !buffer || size < sizeof( mip_t )) return NULL;
 
 	const mip_t *mt = (const mip_t *)buffer;

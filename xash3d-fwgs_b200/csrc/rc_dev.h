@@ -31,6 +31,10 @@ int rc_dev_update_surface_texnums( const int32_t *texnum, int n );
 int rc_dev_upload_blendluts( const uint16_t *alphamap, const uint8_t *addmap, const uint8_t *modmap );
 /* the entities of the next batches as ordered draw items (rc_shared.h); nitems = 0: none */
 int rc_dev_set_items( const rc_item_t *items, int nitems, const rc_corner_t *corners, int ncorners, const rc_sortent_t *sortents, int nsortents );
+/* studio models: the static arena (vertices, normals, bone indices, mesh corners of every submodel used so far; replaces the
+ * previous one) and the per-batch state: drawn (entity, submodel) parts, bone matrices [n][12], bone-space light vectors [n][3] */
+int rc_dev_upload_studio_static( const void *arena, size_t bytes );
+int rc_dev_set_studio( const rc_spart_t *parts, int nparts, const float *bones, int nbones, const float *blightvecs, int totalverts, int totalnorms );
 /* g_lightstylevalue[256] for the next batch (ref/common/ref_light.c:30-87) */
 int rc_dev_set_lightstyles( const int32_t *values );
 /* the active dynamic lights of the next batches (R_PushDlights, ref/common/ref_light.c:170: die >= time, radius != 0);

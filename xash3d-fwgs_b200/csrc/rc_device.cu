@@ -609,6 +609,10 @@ struct Dev
 	int32_t *d_item_order = nullptr; rc_poly_t *d_polys = nullptr;
 	size_t cap_item_order = 0, cap_polys = 0;
 
+	/* studio models */
+	uint8_t *d_sstatic = nullptr; rc_spart_t *d_parts = nullptr; float *d_bones = nullptr, *d_blight = nullptr, *d_mvpos = nullptr; int32_t *d_mlight = nullptr;
+	int nparts = 0, totalverts = 0, totalnorms = 0; size_t cap_mvpos = 0, cap_mlight = 0; bool studio_dirty = false;
+
 	/* dynamic lights of the next batch */
 	rc_dlight_t *d_dlights = nullptr;
 	uint32_t *d_dlightbits = nullptr;
@@ -988,7 +992,7 @@ void rc_dev_shutdown( void )
 	cudaDeviceSynchronize();
 	free_batch();
 	/* everything rc_dev_init / the uploads created, so that R_Shutdown + R_Init (vid_restart) starts clean */
-	void **ptrs[] = { (void **)&D.d_item_order, (void **)&D.d_polys, (void **)&D.d_alphamap, (void **)&D.d_addmap, (void **)&D.d_modmap, (void **)&D.d_items, (void **)&D.d_corners, (void **)&D.d_sortents, (void **)&D.d_display, (void **)&D.d_screenmap, (void **)&D.d_dlights, (void **)&D.d_dlightbits,
+	void **ptrs[] = { (void **)&D.d_sstatic, (void **)&D.d_parts, (void **)&D.d_bones, (void **)&D.d_blight, (void **)&D.d_mvpos, (void **)&D.d_mlight, (void **)&D.d_item_order, (void **)&D.d_polys, (void **)&D.d_alphamap, (void **)&D.d_addmap, (void **)&D.d_modmap, (void **)&D.d_items, (void **)&D.d_corners, (void **)&D.d_sortents, (void **)&D.d_display, (void **)&D.d_screenmap, (void **)&D.d_dlights, (void **)&D.d_dlightbits,
 		(void **)&D.d_colormap, (void **)&D.d_lightgamma, (void **)&D.d_sintable, (void **)&D.d_textures, (void **)&D.d_texels,
 		(void **)&D.d_styles, (void **)&D.d_keys, (void **)&D.d_need, (void **)&D.d_list, (void **)&D.d_nlist,
 		(void **)&D.d_counters, &D.d_flush };
@@ -997,6 +1001,7 @@ void rc_dev_shutdown( void )
 	if( D.h_counters ) { cudaFreeHost( D.h_counters ); D.h_counters = nullptr; }
 	D.cap_cands = D.cap_edges = D.cap_blk_events = 0; D.caps_dirty = false;
 	D.nitems = D.ncorners = D.nsortents = 0; D.h_items.clear(); D.ntris = 0; D.cap_item_order = D.cap_polys = 0;
+	D.nparts = D.totalverts = D.totalnorms = 0; D.cap_mvpos = D.cap_mlight = 0; D.studio_dirty = false;
 	D.display_bytes = 0; D.ndlights = 0; D.screen_bpp = 0; D.cache_texels = 0; D.ntextures = 0;
 	D.sc = rc_scene_t{}; D.h_surfaces.clear(); D.h_textures.clear();
 	cudaStream_t *streams[] = { &D.stream, &D.copy };
@@ -1149,6 +1154,30 @@ int rc_dev_set_items( const rc_item_t *items, int nitems, const rc_corner_t *cor
 	D.ntris = 0;
 	for( int i = 0; i < nitems; i++ ) D.ntris += items[i].count;
 	D.h2d_bytes += sizeof( rc_item_t ) * (size_t)nitems + sizeof( rc_corner_t ) * (size_t)ncorners + sizeof( rc_sortent_t ) * (size_t)nsortents;
+	return 0;
+}
+
+int rc_dev_upload_studio_static( const void *arena, size_t bytes )
+{
+	CK( cudaStreamSynchronize( D.stream ));
+	if( upload( &D.d_sstatic, (const uint8_t *)arena, bytes + 16 > 16 ? bytes : 16 ) != 0 ) return -1;
+	D.h2d_bytes += bytes;
+	return 0;
+}
+
+int rc_dev_set_studio( const rc_spart_t *parts, int nparts, const float *bones, int nbones, const float *blightvecs, int totalverts, int totalnorms )
+{
+	if( !nparts && !D.nparts ) return 0;
+	CK( cudaStreamSynchronize( D.stream ));
+	D.nparts = nparts; D.totalverts = totalverts; D.totalnorms = totalnorms;
+	if( !nparts ) return 0;
+	if( upload( &D.d_parts, parts, (size_t)nparts ) != 0 ) return -1;
+	if( upload( &D.d_bones, bones, (size_t)nbones * 12 ) != 0 ) return -1;
+	if( upload( &D.d_blight, blightvecs, (size_t)nbones * 3 ) != 0 ) return -1;
+	if( (size_t)totalverts * 3 > D.cap_mvpos ) { if( dalloc( &D.d_mvpos, (size_t)totalverts * 3 ) != 0 ) return -1; D.cap_mvpos = (size_t)totalverts * 3; }
+	if( (size_t)totalnorms > D.cap_mlight ) { if( dalloc( &D.d_mlight, (size_t)totalnorms ) != 0 ) return -1; D.cap_mlight = (size_t)totalnorms; }
+	D.h2d_bytes += sizeof( rc_spart_t ) * (size_t)nparts + sizeof( float ) * 15 * (size_t)nbones;
+	D.studio_dirty = true;
 	return 0;
 }
 

@@ -35,6 +35,7 @@
 #include "studio.h"
 #include "triangleapi.h"
 #include "entity_types.h"
+#include "pmove.h"
 
 #include "rc_dev.h"
 #include "ref_cuda.h"
@@ -132,6 +133,18 @@ static struct
 	int          cur_sortent;
 	qboolean     warned[8];
 } rc;
+
+/* studio models of the batch being prepared + the static per-submodel tables (see the studio section) */
+static struct
+{
+	byte   *arena; size_t used, cap; qboolean dirty;
+	struct { const void *hdr, *sub; int skin; int32_t sverts, svertbone, snorms, snormbone, snormflags; int nmesh; int32_t mesh_first[MAXSTUDIOMESHES], mesh_ntris[MAXSTUDIOMESHES], mesh_flags[MAXSTUDIOMESHES], mesh_tex[MAXSTUDIOMESHES]; } sub[256];
+	int     nsub;
+	rc_spart_t *parts; int nparts, maxparts;
+	float  *bones; int nbones, maxbones;      /* matrix3x4 per bone */
+	float  *blight; int maxblight;            /* vec3 per bone */
+	int     totalverts, totalnorms;
+} rs;
 
 static void rc_strncpy( char *dst, const char *src, size_t n ) { strncpy( dst, src, n - 1 ); dst[n - 1] = 0; }
 
@@ -1225,6 +1238,7 @@ static void rc_build_items( void )
 {
 	rc.nitems = rc.ncorners = rc.nsortents = 0;
 	rc.cur_sortent = -1;
+	rs.nparts = rs.nbones = rs.totalverts = rs.totalnorms = 0;
 	rc.tri.blend = 1.0f;
 	rc.tri.drawer = RC_DRAW_FILL;
 	GL_SetRenderMode( kRenderNormal );
@@ -1292,13 +1306,584 @@ static void rc_build_items( void )
 		it->order0 = order;
 		order += it->count;
 	}
+	if( rs.dirty )
+	{
+		RC_CHECK_DEV( rc_dev_upload_studio_static( rs.arena, rs.used ));
+		rs.dirty = false;
+	}
+	RC_CHECK_DEV( rc_dev_set_studio( rs.parts, rs.nparts, rs.bones, rs.nbones, rs.blight, rs.totalverts, rs.totalnorms ));
 	RC_CHECK_DEV( rc_dev_set_items( rc.items, rc.nitems, rc.corners, rc.ncorners, rc.sortents, rc.nsortents ));
+}
+
+/* ---------------------------------------------------------------------------------------------- */
+/* studio models: the per-entity, view-independent half of R_StudioDrawModel (ref/soft/r_studio.c:2720) on the host -
+ * skeleton (quaternion math through the engine's `public` library, as ref_soft itself does), entity lighting
+ * (R_EntityDynamicLight / R_LightVec, ref/common/ref_light.c:222-700) - and static per-submodel tables for the device,
+ * which transforms the vertices by their bones, lights the normals and rasterises the meshes per view.               */
+
+
+static int32_t rs_put( const void *src, size_t bytes, size_t align )
+{
+	size_t at = ( rs.used + align - 1 ) & ~( align - 1 );
+	if( at + bytes > rs.cap )
+	{
+		size_t n = rs.cap ? rs.cap : 1 << 20;
+		while( n < at + bytes ) n *= 2;
+		rs.arena = gEngfuncs._Mem_Realloc( rc.pool, rs.arena, n, true, __FILE__, __LINE__ );
+		rs.cap = n;
+	}
+	memcpy( rs.arena + at, src, bytes );
+	rs.used = at + bytes;
+	rs.dirty = true;
+	return (int32_t)at;
+}
+
+/* the static tables of one submodel with one skin family: vertices, normals, and every mesh's strips / fans unrolled into
+ * triangles the way TriVertex3f assembles them (r_triapi.c:221), texels from TriTexCoord2f on the mesh's skin */
+static int rs_submodel( studiohdr_t *hdr, mstudiomodel_t *sub, int skinnum )
+{
+	for( int i = 0; i < rs.nsub; i++ )
+		if( rs.sub[i].hdr == hdr && rs.sub[i].sub == sub && rs.sub[i].skin == skinnum )
+			return i;
+	if( rs.nsub == 256 || sub->nummesh > MAXSTUDIOMESHES )
+		return -1;
+	const int si = rs.nsub++;
+	rs.sub[si].hdr = hdr; rs.sub[si].sub = sub; rs.sub[si].skin = skinnum;
+	const byte *base = (const byte *)hdr;
+	rs.sub[si].sverts = rs_put( base + sub->vertindex, sizeof( vec3_t ) * sub->numverts, 4 ) / 4;
+	rs.sub[si].snorms = rs_put( base + sub->normindex, sizeof( vec3_t ) * sub->numnorms, 4 ) / 4;
+	rs.sub[si].svertbone = rs_put( base + sub->vertinfoindex, sub->numverts, 4 );
+	rs.sub[si].snormbone = rs_put( base + sub->norminfoindex, sub->numnorms, 4 );
+	const mstudiotexture_t *ptexture = (const mstudiotexture_t *)( base + hdr->textureindex );
+	const short *pskinref = (const short *)( base + hdr->skinindex );
+	if( skinnum > 0 && skinnum < hdr->numskinfamilies )
+		pskinref += skinnum * hdr->numskinref;
+	const mstudiomesh_t *pmesh = (const mstudiomesh_t *)( base + sub->meshindex );
+	byte *nflags = rc_malloc( Q_max( 1, sub->numnorms ));
+	int k = 0;
+	for( int j = 0; j < sub->nummesh; j++ )
+		for( int i = 0; i < pmesh[j].numnorms && k < sub->numnorms; i++, k++ )
+			nflags[k] = (byte)( ptexture[pskinref[pmesh[j].skinref]].flags & 0xFF );
+	rs.sub[si].snormflags = rs_put( nflags, Q_max( 1, sub->numnorms ), 4 );
+	rc_free( nflags );
+	rs.sub[si].nmesh = sub->nummesh;
+	for( int j = 0; j < sub->nummesh; j++ )
+	{
+		const mstudiotexture_t *tx = &ptexture[pskinref[pmesh[j].skinref]];
+		const float fs = 1.0f / (float)tx->width, ft = 1.0f / (float)tx->height;
+		const short *ptricmds = (const short *)( base + pmesh[j].triindex );
+		rc_mcorner_t *out = rc_malloc( sizeof( rc_mcorner_t ) * 3 * Q_max( 1, pmesh[j].numtris + 8 ));
+		int ntris = 0, cap = pmesh[j].numtris + 8, i;
+		/* the texels come out of TriTexCoord2f with the mesh's skin bound */
+		const int keep_w = rc.tri.skinwidth, keep_h = rc.tri.skinheight;
+		rc.tri.skinwidth = tx->width; rc.tri.skinheight = tx->height;
+		while(( i = *( ptricmds++ )))
+		{
+			const int fan = i < 0;
+			if( fan ) i = -i;
+			rc_mcorner_t tv[3];
+			int vertcount = 0, n = 0;
+			for( ; i > 0; i--, ptricmds += 4 )
+			{
+				rc_mcorner_t cv;
+				cv.vert = (uint16_t)ptricmds[0]; cv.norm = (uint16_t)ptricmds[1];
+				if( FBitSet( tx->flags, STUDIO_NF_UV_COORDS )) TriTexCoord2f( HalfToFloat( ptricmds[2] ), HalfToFloat( ptricmds[3] ));
+				else TriTexCoord2f( ptricmds[2] * fs, ptricmds[3] * ft );
+				cv.s = rc.tri.s; cv.t = rc.tri.t;
+				if( ntris + 1 > cap ) continue;
+				if( fan )
+				{
+					tv[vertcount++] = cv;
+					if( vertcount >= 3 )
+					{
+						out[3 * ntris] = tv[0]; out[3 * ntris + 1] = tv[1]; out[3 * ntris + 2] = tv[2]; ntris++;
+						tv[1] = tv[2];
+						vertcount = 2;
+					}
+				}
+				else
+				{
+					tv[n] = cv;
+					n++; vertcount++;
+					if( n == 3 ) n = 0;
+					if( vertcount >= 3 )
+					{
+						if( vertcount & 1 ) { out[3 * ntris] = tv[0]; out[3 * ntris + 1] = tv[1]; out[3 * ntris + 2] = tv[2]; }
+						else { out[3 * ntris] = tv[2]; out[3 * ntris + 1] = tv[1]; out[3 * ntris + 2] = tv[0]; }
+						ntris++;
+					}
+				}
+			}
+		}
+		rc.tri.skinwidth = keep_w; rc.tri.skinheight = keep_h;
+		rs.sub[si].mesh_first[j] = rs_put( out, sizeof( rc_mcorner_t ) * 3 * Q_max( 1, ntris ), 8 ) / (int32_t)sizeof( rc_mcorner_t );
+		rs.sub[si].mesh_ntris[j] = ntris;
+		rs.sub[si].mesh_flags[j] = tx->flags;
+		rs.sub[si].mesh_tex[j] = tx->index;
+		rc_free( out );
+	}
+	return si;
+}
+
+/* slot R_StudioLerpMovement (r_studio.c:491): where a MOVETYPE_STEP entity is between its last two updates */
+static void R_StudioLerpMovement( cl_entity_t *e, double time, vec3_t origin, vec3_t angles )
+{
+	float f = 1.0f;
+	if(( time < e->curstate.animtime + 1.0f ) && ( e->curstate.animtime != e->latched.prevanimtime ))
+		f = ( time - e->curstate.animtime ) / ( e->curstate.animtime - e->latched.prevanimtime );
+	VectorLerp( e->latched.prevorigin, f, e->curstate.origin, origin );
+	if( !VectorCompareEpsilon( e->curstate.angles, e->latched.prevangles, ON_EPSILON ))
+	{
+		vec4_t q, q1, q2;
+		AngleQuaternion( e->curstate.angles, q1, false );
+		AngleQuaternion( e->latched.prevangles, q2, false );
+		QuaternionSlerp( q2, q1, f, q );
+		QuaternionAngle( q, angles );
+	}
+	else VectorCopy( e->curstate.angles, angles );
+}
+
+/* R_StudioEstimateFrame (r_studio.c:557) */
+static float rc_studio_frame( const cl_entity_t *e, const mstudioseqdesc_t *pseqdesc, double time )
+{
+	double dfdt = time < e->curstate.animtime ? 0.0 : ( time - e->curstate.animtime ) * e->curstate.framerate * pseqdesc->fps;
+	double f = pseqdesc->numframes <= 1 ? 0.0 : ( e->curstate.frame * ( pseqdesc->numframes - 1 )) / 256.0;
+	f += dfdt;
+	if( pseqdesc->flags & STUDIO_LOOPING )
+	{
+		if( pseqdesc->numframes > 1 )
+			f -= (int)( f / ( pseqdesc->numframes - 1 )) * ( pseqdesc->numframes - 1 );
+		if( f < 0 ) f += ( pseqdesc->numframes - 1 );
+	}
+	else
+	{
+		if( f >= pseqdesc->numframes - 1.001 ) f = pseqdesc->numframes - 1.001;
+		if( f < 0.0 ) f = 0.0;
+	}
+	return f;
+}
+
+static float R_StudioEstimateFrame( cl_entity_t *e, mstudioseqdesc_t *pseqdesc, double time ) { return rc_studio_frame( e, pseqdesc, time ); }
+
+static float rc_studio_interpolant( const cl_entity_t *e )
+{
+	float dadt = 1.0f;
+	if( e->curstate.animtime >= e->latched.prevanimtime + 0.01f )
+	{
+		dadt = ( gp_cl->time - e->curstate.animtime ) / 0.1f;
+		if( dadt > 2.0f ) dadt = 2.0f;
+	}
+	return dadt;
+}
+
+/* R_StudioCalcRotations (r_studio.c:733) with R_StudioCalcBoneAdj (:668) */
+static void rc_studio_rotations( const cl_entity_t *e, studiohdr_t *hdr, float pos[][3], vec4_t *q, const mstudioseqdesc_t *pseqdesc, const mstudioanim_t *panim, float f )
+{
+	if( f > pseqdesc->numframes - 1 ) f = 0.0f;
+	else if( f < -0.01f ) f = -0.01f;
+	const int frame = (int)f;
+	const float dadt = rc_studio_interpolant( e );
+	const float s = ( f - frame );
+	float adj[MAXSTUDIOCONTROLLERS];
+	const mstudiobonecontroller_t *bc = (const mstudiobonecontroller_t *)((const byte *)hdr + hdr->bonecontrollerindex );
+	float value = 0.0f;
+	for( int j = 0; j < hdr->numbonecontrollers && j < MAXSTUDIOCONTROLLERS; j++ )
+	{
+		const int i = bc[j].index;
+		const byte *c1 = e->curstate.controller, *c2 = e->latched.prevcontroller;
+		if( i == STUDIO_MOUTH )
+		{
+			value = (float)e->mouth.mouthopen / 64.0f;
+			value = bound( 0.0f, value, 1.0f );
+			value = ( 1.0f - value ) * bc[j].start + value * bc[j].end;
+		}
+		else if( i < 4 )
+		{
+			if( FBitSet( bc[j].type, STUDIO_RLOOP ))
+			{
+				if( abs( c1[i] - c2[i] ) > 128 )
+				{
+					const int a = ( c1[i] + 128 ) % 256, b = ( c2[i] + 128 ) % 256;
+					value = (( a * dadt ) + ( b * ( 1.0f - dadt )) - 128 ) * ( 360.0f / 256.0f ) + bc[j].start;
+				}
+				else value = (( c1[i] * dadt + ( c2[i] ) * ( 1.0f - dadt ))) * ( 360.0f / 256.0f ) + bc[j].start;
+			}
+			else
+			{
+				value = ( c1[i] * dadt + c2[i] * ( 1.0f - dadt )) / 255.0f;
+				value = bound( 0.0f, value, 1.0f );
+				value = ( 1.0f - value ) * bc[j].start + value * bc[j].end;
+			}
+		}
+		switch( bc[j].type & STUDIO_TYPES )
+		{
+		case STUDIO_XR: case STUDIO_YR: case STUDIO_ZR: adj[j] = DEG2RAD( value ); break;
+		case STUDIO_X: case STUDIO_Y: case STUDIO_Z: adj[j] = value; break;
+		}
+	}
+	const mstudiobone_t *pbone = (const mstudiobone_t *)((const byte *)hdr + hdr->boneindex );
+	for( int i = 0; i < hdr->numbones; i++, pbone++, panim++ )
+		R_StudioCalcBones( frame, s, pbone, panim, adj, pos[i], q[i] );
+	if( pseqdesc->motiontype & STUDIO_X ) pos[pseqdesc->motionbone][0] = 0.0f;
+	if( pseqdesc->motiontype & STUDIO_Y ) pos[pseqdesc->motionbone][1] = 0.0f;
+	if( pseqdesc->motiontype & STUDIO_Z ) pos[pseqdesc->motionbone][2] = 0.0f;
+}
+
+/* R_StudioSetUpTransform + R_StudioSetupBones (r_studio.c:523,840): bone and light matrices of the entity */
+static qboolean rc_studio_skeleton( cl_entity_t *e, studiohdr_t *hdr, matrix3x4 rotation, matrix3x4 *bones, matrix3x4 *light )
+{
+	static vec3_t pos[MAXSTUDIOBONES], pos2[MAXSTUDIOBONES], pos3[MAXSTUDIOBONES], pos4[MAXSTUDIOBONES], pos1b[MAXSTUDIOBONES];
+	static vec4_t q[MAXSTUDIOBONES], q2[MAXSTUDIOBONES], q3[MAXSTUDIOBONES], q4[MAXSTUDIOBONES], q1b[MAXSTUDIOBONES];
+	vec3_t origin, angles;
+	VectorCopy( e->origin, origin ); VectorCopy( e->angles, angles );
+	if( e->curstate.movetype == MOVETYPE_STEP && !FBitSet( gp_host->features, ENGINE_COMPUTE_STUDIO_LERP ))
+		R_StudioLerpMovement( e, gp_cl->time, origin, angles );
+	if( !FBitSet( gp_host->features, ENGINE_COMPENSATE_QUAKE_BUG ))
+		angles[PITCH] = -angles[PITCH];
+	Matrix3x4_CreateFromEntity( rotation, angles, origin, 1.0f );
+
+	if( e->curstate.sequence >= hdr->numseq ) e->curstate.sequence = 0;
+	const int nb = hdr->numbones;
+	const double time = gp_cl->time;
+	mstudioseqdesc_t *pseqdesc = (mstudioseqdesc_t *)((byte *)hdr + hdr->seqindex ) + e->curstate.sequence;
+	const float f = rc_studio_frame( e, pseqdesc, time );
+	mstudioanim_t *panim = gEngfuncs.R_StudioGetAnim( hdr, e->model, pseqdesc );
+	if( !panim )
+		return false;
+	rc_studio_rotations( e, hdr, pos, q, pseqdesc, panim, f );
+	if( pseqdesc->numblends > 1 )
+	{
+		panim += nb;
+		rc_studio_rotations( e, hdr, pos2, q2, pseqdesc, panim, f );
+		const float dadt = rc_studio_interpolant( e );
+		float s = ( e->curstate.blending[0] * dadt + e->latched.prevblending[0] * ( 1.0f - dadt )) / 255.0f;
+		R_StudioSlerpBones( nb, q, pos, q2, pos2, s );
+		if( pseqdesc->numblends == 4 )
+		{
+			panim += nb; rc_studio_rotations( e, hdr, pos3, q3, pseqdesc, panim, f );
+			panim += nb; rc_studio_rotations( e, hdr, pos4, q4, pseqdesc, panim, f );
+			s = ( e->curstate.blending[0] * dadt + e->latched.prevblending[0] * ( 1.0f - dadt )) / 255.0f;
+			R_StudioSlerpBones( nb, q3, pos3, q4, pos4, s );
+			s = ( e->curstate.blending[1] * dadt + e->latched.prevblending[1] * ( 1.0f - dadt )) / 255.0f;
+			R_StudioSlerpBones( nb, q, pos, q3, pos3, s );
+		}
+	}
+	if( e->latched.sequencetime && ( e->latched.sequencetime + 0.2f > time ) && ( e->latched.prevsequence < hdr->numseq ))
+	{
+		/* blend from the previous sequence */
+		pseqdesc = (mstudioseqdesc_t *)((byte *)hdr + hdr->seqindex ) + e->latched.prevsequence;
+		panim = gEngfuncs.R_StudioGetAnim( hdr, e->model, pseqdesc );
+		if( !panim ) return false;
+		rc_studio_rotations( e, hdr, pos1b, q1b, pseqdesc, panim, e->latched.prevframe );
+		if( pseqdesc->numblends > 1 )
+		{
+			panim += nb; rc_studio_rotations( e, hdr, pos2, q2, pseqdesc, panim, e->latched.prevframe );
+			float s = ( e->latched.prevseqblending[0] ) / 255.0f;
+			R_StudioSlerpBones( nb, q1b, pos1b, q2, pos2, s );
+			if( pseqdesc->numblends == 4 )
+			{
+				panim += nb; rc_studio_rotations( e, hdr, pos3, q3, pseqdesc, panim, e->latched.prevframe );
+				panim += nb; rc_studio_rotations( e, hdr, pos4, q4, pseqdesc, panim, e->latched.prevframe );
+				s = ( e->latched.prevseqblending[0] ) / 255.0f;
+				R_StudioSlerpBones( nb, q3, pos3, q4, pos4, s );
+				s = ( e->latched.prevseqblending[1] ) / 255.0f;
+				R_StudioSlerpBones( nb, q1b, pos1b, q3, pos3, s );
+			}
+		}
+		const float s = 1.0f - ( time - e->latched.sequencetime ) / 0.2f;
+		R_StudioSlerpBones( nb, q, pos, q1b, pos1b, s );
+	}
+	else e->latched.prevframe = f;
+
+	const mstudiobone_t *pbones = (const mstudiobone_t *)((const byte *)hdr + hdr->boneindex );
+	for( int i = 0; i < nb; i++ )
+	{
+		matrix3x4 bonematrix;
+		Matrix3x4_FromOriginQuat( bonematrix, q[i], pos[i] );
+		if( pbones[i].parent == -1 )
+		{
+			Matrix3x4_ConcatTransforms( bones[i], rotation, bonematrix );
+			Matrix3x4_Copy( light[i], bones[i] );
+			if( e->curstate.renderfx == kRenderFxExplode )
+			{
+				float scale = 1.0f + ( time - e->curstate.animtime ) * 10.0f;
+				if( scale > 2.0f ) scale = 2.0f;
+				bones[i][0][1] *= scale; bones[i][1][1] *= scale; bones[i][2][1] *= scale;
+			}
+		}
+		else
+		{
+			Matrix3x4_ConcatTransforms( bones[i], bones[pbones[i].parent], bonematrix );
+			Matrix3x4_ConcatTransforms( light[i], light[pbones[i].parent], bonematrix );
+		}
+	}
+	return true;
+}
+
+/* R_RecursiveLightPoint (ref/common/ref_light.c:222) over the world's nodes: the first lightmapped face a segment hits */
+static vec3_t rs_lightspot, rs_lightvec;
+
+static qboolean rc_light_trace( model_t *model, mnode_t *node, const vec3_t start, const vec3_t end, uint *cv )
+{
+	while( node && node->contents >= 0 )
+	{
+		const float front = PlaneDiff( start, node->plane ), back = PlaneDiff( end, node->plane );
+		const int side = front < 0;
+		if(( back < 0 ) == side )
+		{
+			node = node_child( node, side, model );
+			continue;
+		}
+		const float frac = front / ( front - back );
+		vec3_t mid;
+		VectorLerp( start, frac, end, mid );
+		if( rc_light_trace( model, node_child( node, side, model ), start, mid, cv ))
+			return true;
+		const int firstsurface = node_firstsurface( node, model ), numsurfaces = node_numsurfaces( node, model );
+		VectorCopy( mid, rs_lightspot );
+		for( int i = 0; i < numsurfaces; i++ )
+		{
+			const msurface_t *surf = &model->surfaces[firstsurface + i];
+			const mextrasurf_t *info = surf->info;
+			if( FBitSet( surf->flags, SURF_DRAWTILED ))
+				continue;
+			const float s = DotProduct( mid, info->lmvecs[0] ) + info->lmvecs[0][3];
+			const float t = DotProduct( mid, info->lmvecs[1] ) + info->lmvecs[1][3];
+			if( s < info->lightmapmins[0] || t < info->lightmapmins[1] )
+				continue;
+			float ds = s - info->lightmapmins[0], dt = t - info->lightmapmins[1];
+			if( ds > info->lightextents[0] || dt > info->lightextents[1] )
+				continue;
+			cv[0] = cv[1] = cv[2] = 0;
+			if( !surf->samples )
+				return true;
+			const int sample_size = gEngfuncs.Mod_SampleSizeForFace( surf );
+			const int smax = ( info->lightextents[0] / sample_size ) + 1, tmax = ( info->lightextents[1] / sample_size ) + 1;
+			ds /= sample_size; dt /= sample_size;
+			const color24 *lm = surf->samples + Q_rint( dt ) * smax + Q_rint( ds );
+			if( info->deluxemap && !rc.warned[6] ) { rc.warned[6] = true; gEngfuncs.Con_Reportf( "ref_cuda: deluxe maps are not used for entity light vectors\n" ); }
+			for( int map = 0; map < MAXLIGHTMAPS && surf->styles[map] != 255; map++ )
+			{
+				const uint scale = rc.lightstylevalue[surf->styles[map]];
+				cv[0] += lm->r * scale; cv[1] += lm->g * scale; cv[2] += lm->b * scale;
+				lm += smax * tmax;
+			}
+			return true;
+		}
+		/* go down the back side */
+		return rc_light_trace( model, node_child( node, !side, model ), mid, end, cv );
+	}
+	cv[0] = cv[1] = cv[2] = 0;
+	return false;
+}
+
+/* R_LightVec (ref_light.c:450) against the world (the first physent): light colour 0..255 per channel */
+static void rc_light_vec( const vec3_t start, const vec3_t end, qboolean want_vec, uint *light )
+{
+	light[0] = light[1] = light[2] = 0;
+	VectorClear( rs_lightspot ); VectorClear( rs_lightvec );
+	model_t *world = gp_cl->models[1];
+	if( !world || !world->lightdata ) { light[0] = light[1] = light[2] = 255; return; }
+	for( int pass = 0; pass < 2; pass++ )
+	{
+		uint cv[3];
+		mnode_t *pnodes = &world->nodes[world->hulls[0].firstclipnode];
+		vec3_t offset, s_l, e_l;
+		VectorSubtract( world->hulls[0].clip_mins, vec3_origin, offset );
+		VectorSubtract( pass ? end : start, offset, s_l );
+		VectorSubtract( pass ? start : end, offset, e_l );
+		if( rc_light_trace( world, pnodes, s_l, e_l, cv ))
+		{
+			light[0] = Q_min(( cv[0] >> 8 ), 255 ); light[1] = Q_min(( cv[1] >> 8 ), 255 ); light[2] = Q_min(( cv[2] >> 8 ), 255 );
+		}
+		/* nothing lit below: r_lighting_extended tries the ceiling when the caller asked for the light vector */
+		if(( light[0] + light[1] + light[2] ) != 0 || !want_vec || !gEngfuncs.pfnGetCvarFloat( "r_lighting_extended" ))
+			break;
+	}
+}
+
+/* R_EntityDynamicLight (ref_light.c:498): ambient / shade light, colour and direction for a model */
+/* (alight_t.ambientlight / shadelight are ints, common/com_model.h:405: the float results are truncated into them) */
+static void rc_entity_light( cl_entity_t *ent, int *ambientlight, int *shadelight, vec3_t color, vec3_t plightvec )
+{
+	if( r_fullbright->value || FBitSet( ent->curstate.effects, EF_FULLBRIGHT ))
+	{
+		*shadelight = 0; *ambientlight = 192;
+		VectorSet( plightvec, 0.0f, 0.0f, -1.0f ); VectorSet( color, 1.0f, 1.0f, 1.0f );
+		return;
+	}
+	const movevars_t *mv = (const movevars_t *)gEngfuncs.EngineGetParm( PARM_GET_MOVEVARS_PTR, 0 );
+	vec3_t lightDir, origin, vecSrc, vecEnd;
+	if( FBitSet( ent->curstate.effects, EF_INVLIGHT )) VectorSet( lightDir, 0.0f, 0.0f, 1.0f );
+	else VectorSet( lightDir, 0.0f, 0.0f, -1.0f );
+	VectorCopy( ent->origin, origin );
+	VectorSet( vecSrc, origin[0], origin[1], origin[2] - lightDir[2] * 8.0f );
+	uint light[3] = { 0, 0, 0 };
+	if( mv && ( mv->skycolor[0] + mv->skycolor[1] + mv->skycolor[2] ) != 0 && !rc.warned[7] )
+	{
+		rc.warned[7] = true;
+		gEngfuncs.Con_Reportf( "ref_cuda: sky light on models (movevars skycolor) is not built\n" );
+	}
+	VectorScale( lightDir, 2048.0f, vecEnd );
+	VectorAdd( vecEnd, vecSrc, vecEnd );
+	rc_light_vec( vecSrc, vecEnd, true, light );
+	/* no deluxe data: the light vector is null and the direction comes from the gradient of the floor light */
+	{
+		float grad[4];
+		uint g[3];
+		vecSrc[0] -= 16.0f; vecSrc[1] -= 16.0f; vecEnd[0] -= 16.0f; vecEnd[1] -= 16.0f;
+		rc_light_vec( vecSrc, vecEnd, false, g ); grad[0] = ( g[0] + g[1] + g[2] ) / 768.0f;
+		vecSrc[0] += 32.0f; vecEnd[0] += 32.0f;
+		rc_light_vec( vecSrc, vecEnd, false, g ); grad[1] = ( g[0] + g[1] + g[2] ) / 768.0f;
+		vecSrc[1] += 32.0f; vecEnd[1] += 32.0f;
+		rc_light_vec( vecSrc, vecEnd, false, g ); grad[2] = ( g[0] + g[1] + g[2] ) / 768.0f;
+		vecSrc[0] -= 32.0f; vecEnd[0] -= 32.0f;
+		rc_light_vec( vecSrc, vecEnd, false, g ); grad[3] = ( g[0] + g[1] + g[2] ) / 768.0f;
+		lightDir[0] = grad[0] - grad[1] - grad[2] + grad[3];
+		lightDir[1] = grad[1] + grad[0] - grad[2] - grad[3];
+		VectorNormalize( lightDir );
+	}
+	if( ent->curstate.renderfx == kRenderFxLightMultiplier && ent->curstate.iuser4 != 10 )
+	{
+		light[0] *= ent->curstate.iuser4 / 10.0f; light[1] *= ent->curstate.iuser4 / 10.0f; light[2] *= ent->curstate.iuser4 / 10.0f;
+	}
+	vec3_t finalLight = { light[0], light[1], light[2] };
+	ent->cvFloorColor.r = light[0]; ent->cvFloorColor.g = light[1]; ent->cvFloorColor.b = light[2]; ent->cvFloorColor.a = 0;
+	float total = Q_max( Q_max( light[0], light[1] ), light[2] );
+	if( total == 0.0f ) total = 1.0f;
+	VectorScale( lightDir, total, lightDir );
+	const dlight_t *dls = (const dlight_t *)gEngfuncs.EngineGetParm( PARM_GET_DLIGHTS_PTR, 0 );
+	for( uint lnum = 0; dls && lnum < MAX_DLIGHTS; lnum++ )
+	{
+		const dlight_t *dl = &dls[lnum];
+		if( dl->die < gp_cl->time || !r_dynamic->value )
+			continue;
+		vec3_t dist;
+		VectorSubtract( ent->origin, dl->origin, dist );
+		const float radius = VectorLength( dist );
+		const float add = ( dl->radius - radius );
+		if( add > 0.0f )
+		{
+			total += add;
+			if( radius > 1.0f ) VectorScale( dist, ( add / radius ), dist );
+			else VectorScale( dist, add, dist );
+			VectorAdd( lightDir, dist, lightDir );
+			finalLight[0] += dl->color.r * ( add / 256.0f );
+			finalLight[1] += dl->color.g * ( add / 256.0f );
+			finalLight[2] += dl->color.b * ( add / 256.0f );
+		}
+	}
+	float scale;
+	if( ent->model->type == mod_studio && FBitSet( ent->model->flags, STUDIO_AMBIENT_LIGHT )) scale = 0.6f;
+	else scale = bound( 0.75f, v_direct->value, 1.0f );
+	VectorScale( lightDir, scale, lightDir );
+	*shadelight = VectorLength( lightDir );
+	*ambientlight = total - *shadelight;
+	total = Q_max( Q_max( finalLight[0], finalLight[1] ), finalLight[2] );
+	if( total > 0.0f )
+	{
+		color[0] = finalLight[0] * ( 1.0f / total ); color[1] = finalLight[1] * ( 1.0f / total ); color[2] = finalLight[2] * ( 1.0f / total );
+	}
+	else VectorSet( color, 1.0f, 1.0f, 1.0f );
+	if( *ambientlight > 128 ) *ambientlight = 128;
+	if( *ambientlight + *shadelight > 255 ) *shadelight = 255 - *ambientlight;
+	VectorNormalize2( lightDir, plightvec );
 }
 
 static void rc_add_studio( cl_entity_t *e )
 {
-	(void)e;
-	if( !rc.warned[5] ) { rc.warned[5] = true; gEngfuncs.Con_Reportf( "ref_cuda: studio models are not drawn yet\n" ); }
+	studiohdr_t *hdr = (studiohdr_t *)gEngfuncs.Mod_Extradata( mod_studio, e->model );
+	if( !hdr )
+		return;
+	if( e->player || e->curstate.movetype == MOVETYPE_FOLLOW || e->curstate.renderfx == kRenderFxGlowShell || e->curstate.renderfx == kRenderFxDeadPlayer
+		|| FBitSet( hdr->flags, STUDIO_HAS_BONEWEIGHTS ) || hdr->numbones > MAXSTUDIOBONES )
+	{
+		if( !rc.warned[5] ) { rc.warned[5] = true; gEngfuncs.Con_Reportf( "ref_cuda: player models, attached (MOVETYPE_FOLLOW) models, glow shells and bone-weighted models are not drawn yet\n" ); }
+		return;
+	}
+	if( hdr->numbodyparts == 0 )
+		return;
+	static matrix3x4 bones[MAXSTUDIOBONES], light[MAXSTUDIOBONES];
+	matrix3x4 rotation;
+	if( !rc_studio_skeleton( e, hdr, rotation, bones, light ))
+		return;
+	/* attachments of a model that has none: the entity origin (R_StudioClientEvents, r_studio.c:2172) */
+	if( hdr->numattachments <= 0 && gp_cl->time != gp_cl->oldtime )
+		for( int i = 0; i < 4; i++ ) Matrix3x4_OriginFromMatrix( rotation, e->attachment[i] );
+	int ambientlight, shadelight;
+	vec3_t lightcolor, plightvec;
+	rc_entity_light( e, &ambientlight, &shadelight, lightcolor, plightvec );
+
+	/* the entity's bones and bone-space light vectors (R_StudioSetupLighting, r_studio.c:1361) join the batch */
+	const int nb = hdr->numbones, bone0 = rs.nbones;
+	rs.bones = rc_grow( rs.bones, &rs.maxbones, ( bone0 + nb ) * 12, sizeof( float ));
+	rs.blight = rc_grow( rs.blight, &rs.maxblight, ( bone0 + nb ) * 3, sizeof( float ));
+	const float scale = e->curstate.scale;
+	for( int i = 0; i < nb; i++ )
+	{
+		memcpy( rs.bones + ( bone0 + i ) * 12, bones[i], sizeof( matrix3x4 ));
+		vec3_t bl;
+		Matrix3x4_VectorIRotate( light[i], plightvec, bl );
+		if( scale > 1.0f ) VectorNormalize( bl );
+		VectorCopy( bl, rs.blight + ( bone0 + i ) * 3 );
+	}
+	rs.nbones += nb;
+
+	int rendermode = e->curstate.rendermode;
+	if( rendermode > kRenderTransAdd ) rendermode = 0; /* R_StudioSetupRenderer's clamp applies to g_studio.rendermode only; the bind uses the entity's */
+	rendermode = e->curstate.rendermode;
+	const mstudiobodyparts_t *bp0 = (const mstudiobodyparts_t *)((const byte *)hdr + hdr->bodypartindex );
+	for( int b = 0; b < hdr->numbodyparts; b++ )
+	{
+		const mstudiobodyparts_t *bp = bp0 + b;
+		int index = e->curstate.body / bp->base;
+		index = index % bp->nummodels;
+		mstudiomodel_t *sub = (mstudiomodel_t *)((byte *)hdr + bp->modelindex ) + index;
+		const int si = rs_submodel( hdr, sub, e->curstate.skin );
+		if( si < 0 )
+			continue;
+		rs.parts = rc_grow( rs.parts, &rs.maxparts, rs.nparts + 1, sizeof( rc_spart_t ));
+		rc_spart_t *pt = &rs.parts[rs.nparts++];
+		memset( pt, 0, sizeof( *pt ));
+		pt->vert_base = rs.totalverts; pt->numverts = sub->numverts;
+		pt->light_base = rs.totalnorms; pt->numnorms = sub->numnorms;
+		pt->sverts = rs.sub[si].sverts; pt->svertbone = rs.sub[si].svertbone;
+		pt->snorms = rs.sub[si].snorms; pt->snormbone = rs.sub[si].snormbone; pt->snormflags = rs.sub[si].snormflags;
+		pt->bones = bone0; pt->blightvec = bone0;
+		pt->ambientlight = ambientlight; pt->shadelight = shadelight; VectorCopy( lightcolor, pt->lightcolor );
+		pt->blend = rc.tri.blend; pt->transadd = rendermode == kRenderTransAdd;
+		rs.totalverts += sub->numverts; rs.totalnorms += sub->numnorms;
+
+		/* GL_StudioSetRenderMode + R_StudioDrawPoints' mesh loop: one draw item per mesh, skin bound under the entity's mode */
+		GL_SetRenderMode( rendermode );
+		int order[MAXSTUDIOMESHES];
+		for( int j = 0; j < rs.sub[si].nmesh; j++ ) order[j] = j;
+		/* r_studio_sort_textures: opaque meshes first, then masked, then additive (R_StudioMeshCompare, r_studio.c:1667);
+		 * insertion sort keeps equal ones in file order, as the reference's comparison of unequal flags needs */
+		for( int a = 1; a < rs.sub[si].nmesh; a++ )
+			for( int c = a; c > 0; c-- )
+			{
+				const int fa = rs.sub[si].mesh_flags[order[c - 1]], fb = rs.sub[si].mesh_flags[order[c]];
+				const int ka = FBitSet( fa, STUDIO_NF_ADDITIVE ) ? 2 : FBitSet( fa, STUDIO_NF_MASKED ) ? 1 : 0;
+				const int kb = FBitSet( fb, STUDIO_NF_ADDITIVE ) ? 2 : FBitSet( fb, STUDIO_NF_MASKED ) ? 1 : 0;
+				if( ka <= kb ) break;
+				const int tmp = order[c]; order[c] = order[c - 1]; order[c - 1] = tmp;
+			}
+		for( int jj = 0; jj < rs.sub[si].nmesh; jj++ )
+		{
+			const int j = order[jj];
+			if( FBitSet( rs.sub[si].mesh_flags[j], STUDIO_NF_CHROME ))
+			{
+				if( !rc.warned[5] ) { rc.warned[5] = true; gEngfuncs.Con_Reportf( "ref_cuda: chrome meshes are not drawn yet\n" ); }
+				continue;
+			}
+			GL_Bind( XASH_TEXTURE0, rs.sub[si].mesh_tex[j] );
+			rc_item_t *it = rc_new_item( RC_ITEM_MESH );
+			it->first = rs.sub[si].mesh_first[j];
+			it->count = rs.sub[si].mesh_ntris[j];
+			it->vert_base = pt->vert_base; it->light_base = pt->light_base;
+		}
+	}
 }
 
 static void rc_prepare_batch( void )
@@ -1584,8 +2169,6 @@ static void R_DecalShoot( int textureIndex, int entityIndex, int modelIndex, vec
 static void R_DecalRemoveAll( int texture ) { (void)texture; }
 static int R_CreateDecalList( struct decallist_s *pList ) { (void)pList; return 0; }
 static void R_ClearAllDecals( void ) {}
-static float R_StudioEstimateFrame( cl_entity_t *e, mstudioseqdesc_t *pseqdesc, double time ) { (void)e; (void)pseqdesc; (void)time; return 0.0f; }
-static void R_StudioLerpMovement( cl_entity_t *e, double time, vec3_t origin, vec3_t angles ) { (void)time; VectorCopy( e->origin, origin ); VectorCopy( e->angles, angles ); }
 static qboolean R_StudioFillAPI( struct engine_studio_api_s *api, struct r_studio_interface_s *pDefaultDraw ) { (void)api; (void)pDefaultDraw; return false; }
 static void R_StudioSetDrawInterface( struct r_studio_interface_s *pDraw ) { (void)pDraw; }
 static void R_SetSkyCloudsTextures( int solidskyTexture, int alphaskyTexture ) { (void)solidskyTexture; (void)alphaskyTexture; }
@@ -1597,7 +2180,38 @@ static qboolean Mod_ProcessRenderData( model_t *mod, qboolean create, const byte
 		return false;
 	return true;
 }
-static void Mod_StudioLoadTextures( model_t *mod, void *data ) { (void)mod; (void)data; }
+/* slot Mod_StudioLoadTextures (ref/soft/r_studio.c:3005-3115): every skin of a studio model goes through the engine's
+ * image loader ("#model/skin.mdl" names tell it the buffer is an mstudiotexture_t whose pixels sit at the announced
+ * pointer) into the texture table; mstudiotexture_t.index becomes the texture number the meshes bind */
+static void Mod_StudioLoadTextures( model_t *mod, void *data )
+{
+	studiohdr_t *phdr = (studiohdr_t *)data;
+	if( !phdr || phdr->textureindex <= 0 )
+		return;
+	mstudiotexture_t *ptexture = (mstudiotexture_t *)((byte *)phdr + phdr->textureindex );
+	char mdlname[128], texname[300], *dot;
+	rc_strncpy( mdlname, mod->name, sizeof( mdlname ));
+	if(( dot = strrchr( mdlname, '.' )) != NULL ) *dot = 0;
+	for( int i = 0; i < phdr->numtextures; i++ )
+	{
+		mstudiotexture_t *tx = &ptexture[i];
+		int flags = 0;
+		if( FBitSet( tx->flags, STUDIO_NF_NORMALMAP )) flags |= TF_NORMALMAP;
+		if( FBitSet( tx->flags, STUDIO_NF_NOMIPS )) flags |= TF_NOMIPMAP;
+		if( !strncasecmp( tx->name, "DM_Base", 7 ) || !strncasecmp( tx->name, "remap", 5 ))
+			SetBits( tx->flags, STUDIO_NF_COLORMAP ); /* player colour remapping itself is not built */
+		const char *base = strrchr( tx->name, '/' );
+		char name[64];
+		rc_strncpy( name, base ? base + 1 : tx->name, sizeof( name ));
+		if(( dot = strrchr( name, '.' )) != NULL ) *dot = 0;
+		gEngfuncs.Image_SetMDLPointer((byte *)phdr + tx->index );
+		snprintf( texname, sizeof( texname ), "#%s/%s.mdl", mdlname, name );
+		const size_t size = sizeof( mstudiotexture_t ) + tx->width * tx->height + 768;
+		tx->index = GL_LoadTexture( texname, (byte *)tx, size, flags );
+		if( !tx->index )
+			tx->index = GL_FindTexture( REF_DEFAULT_TEXTURE );
+	}
+}
 static void CL_DrawParticles( double frametime, particle_t *particles, float partsize ) { (void)frametime; (void)particles; (void)partsize; }
 static void CL_DrawTracers( double frametime, particle_t *tracers ) { (void)frametime; (void)tracers; }
 static void CL_DrawBeams( int fTrans, BEAM *beams ) { (void)fTrans; (void)beams; }

@@ -193,6 +193,28 @@ typedef struct
 	int32_t pad[2];
 } rc_item_t; /* 160 B */
 
+/* a studio submodel as the device keeps it (static per model file): R_StudioDrawPoints' inputs (ref/soft/r_studio.c:1802) */
+typedef struct
+{
+	uint16_t vert, norm; /* indices into the submodel's vertices / the submodel's normals (tricmds, r_studio.c:1685) */
+	int16_t  s, t;       /* TriTexCoord2f's texel for this strip vertex on the mesh's skin */
+} rc_mcorner_t; /* 8 B */
+
+/* one drawn (entity, submodel) of a batch: what k_studio_points needs to transform its vertices and light its normals */
+typedef struct
+{
+	int32_t vert_base, numverts;   /* slice of the batch's transformed vertices */
+	int32_t light_base, numnorms;  /* slice of the batch's per-normal lights */
+	int32_t sverts, svertbone;     /* static arena offsets (floats / bytes): studio vertices, their bones */
+	int32_t snorms, snormbone, snormflags; /* studio normals, their bones, the face flags of the mesh that owns each normal */
+	int32_t bones;                 /* first matrix3x4 of the entity in the batch's bone array (12 floats each) */
+	int32_t blightvec;             /* first vec3 of the entity's bone-space light vectors */
+	float   ambientlight, shadelight, lightcolor[3];
+	float   blend;                 /* tr.blend */
+	int32_t transadd;              /* the entity draws in kRenderTransAdd: every light value is tr.blend */
+	int32_t pad[2];
+} rc_spart_t; /* 80 B */
+
 /* a translucent entity: R_TransEntityCompare's inputs (r_main.c:157-200) */
 typedef struct
 {

@@ -500,6 +500,61 @@ RC_HD void rc_tri_shade( const rc_blendluts_t *L, int drawer, uint32_t color, ui
 }
 
 /* ------------------------------------------------------------------------------------------ */
+/* studio models: R_StudioDrawPoints' per-vertex and per-normal work (ref/soft/r_studio.c:1802-1895)  */
+
+/* Matrix3x4_VectorTransform (public/xash3d_mathlib.h:255): a studio vertex through its bone */
+RC_HD void rc_studio_vertex( const float *m, const float *v, float *out )
+{
+	out[0] = v[0] * m[0] + v[1] * m[1] + v[2] * m[2] + m[3];
+	out[1] = v[0] * m[4] + v[1] * m[5] + v[2] * m[6] + m[7];
+	out[2] = v[0] * m[8] + v[1] * m[9] + v[2] * m[10] + m[11];
+}
+
+/* R_StudioLighting (r_studio.c:1391) for one normal, then what R_StudioSetColorBegin / TriColor4ub / _TriColor4f
+ * (r_studio.c:1509, r_triapi.c:83-141) make of it: the light level (<< 8) every strip vertex with this normal gets */
+RC_HD int32_t rc_studio_light( const rc_spart_t *pt, int flags, const float *normal, const float *blightvec, const uint16_t *lightgamma )
+{
+	float lv[3];
+	if( pt->transadd )
+		lv[0] = lv[1] = lv[2] = pt->blend;
+	else
+	{
+		float l;
+		if( flags & 0x0004 ) /* STUDIO_NF_FULLBRIGHT */
+			l = 1.0f;
+		else
+		{
+			float illum = pt->ambientlight;
+			if( flags & 0x0001 ) /* STUDIO_NF_FLATSHADE */
+				illum += pt->shadelight * 0.8f;
+			else
+			{
+				float lightcos = rc_dot3( normal, blightvec );
+				if( lightcos > 1.0f ) lightcos = 1.0f;
+				illum += pt->shadelight;
+				const float r = 1.4953241f; /* SHADE_LAMBERT */
+				lightcos = ( lightcos + ( r - 1.0f )) / r;
+				if( lightcos > 0.0f ) illum -= pt->shadelight * lightcos;
+				illum = illum > 0.0f ? illum : 0.0f;
+			}
+			illum = illum < 255.0f ? illum : 255.0f;
+			const uint32_t b = (uint32_t)( illum * 4 );
+			l = (float)( b >= 1024 ? 0u : (uint32_t)lightgamma[b] ) / 1023.0f;
+		}
+		lv[0] = pt->lightcolor[0] * l; lv[1] = pt->lightcolor[1] * l; lv[2] = pt->lightcolor[2] * l;
+	}
+	float rgb[3];
+	for( int i = 0; i < 3; i++ )
+	{
+		const uint32_t c = (uint32_t)rc_f2i( lv[i] * 255.0f ) & 0xFFu; /* float -> byte */
+		rgb[i] = (float)c * ( 1.0f / 255.0f );
+	}
+	uint32_t light = (uint32_t)rc_f2i(( rgb[0] + rgb[1] + rgb[2] ) * 31 / 3 );
+	if( light > 31 ) light = 31;
+	return (int32_t)( light << 8 );
+}
+
+/* ------------------------------------------------------------------------------------------ */
 /* draw items -> world-space corners                                                            */
 
 /* R_DrawSpriteModel's orientation switch + R_DrawSpriteQuad (ref/soft/r_sprite.c:120-266) for one view: the four

@@ -104,6 +104,15 @@ class Renderer:
             raise RuntimeError("xh_create_sprite failed")
         return mi
 
+    def load_studio(self, name, mdl: bytes):
+        """A studio model from an MDL v10 file image (tools/mdlgen.py writes synthetic ones).  -> model index"""
+        L = self.host.lib
+        L.xh_load_studio.argtypes = [C.c_char_p, C.c_char_p, C.c_size_t]
+        mi = L.xh_load_studio(name.encode(), mdl, len(mdl))
+        if mi <= 0:
+            raise RuntimeError("xh_load_studio failed")
+        return mi
+
     def add_entity(self, modelindex, origin, angles=(0, 0, 0), rendermode=0, renderamt=255, rendercolor=(0, 0, 0), renderfx=0,
                    frame=0, sequence=0, body=0, skin=0, scale=1.0, framerate=1.0, animtime=0.0, movetype=0, aiment=0):
         ip = (C.c_int * 13)(modelindex, rendermode, renderamt, *[int(c) for c in rendercolor], renderfx, frame, sequence, body, skin, movetype, aiment)
