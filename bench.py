@@ -44,9 +44,9 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
-    ap.add_argument("--config", default=None, choices=["c2", "c3", "c5"],
+    ap.add_argument("--config", default=None, choices=["c2", "c3", "c4", "c5"],
                     help="BASELINE.json config: c2 = 256 views/GPU 320x240 Map S (default at 1 GPU), c3 = 1920x1080 views of Map L with "
-                         "light styles changing every step (surface cache rebuilt per step), c5 = 4096 views/GPU 320x240 Map S with water (default at > 1 GPU)")
+                         "light styles changing every step (surface cache rebuilt per step), c4 = c2's batch with 64 skinned 32-bone studio models, c5 = 4096 views/GPU 320x240 Map S with water (default at > 1 GPU)")
     ap.add_argument("--views", type=int, default=None, help="views per GPU per step")
     ap.add_argument("--width", type=int, default=None)
     ap.add_argument("--height", type=int, default=None)
@@ -56,13 +56,15 @@ def parse_args():
     a = ap.parse_args()
     if a.config is None:
         a.config = "c2" if a.gpus <= 1 else "c5"
-    preset = {"c2": (256, 320, 240, "small"), "c3": (8, 1920, 1080, "large"), "c5": (4096, 320, 240, "small")}[a.config]
+    preset = {"c2": (256, 320, 240, "small"), "c3": (8, 1920, 1080, "large"), "c4": (256, 320, 240, "small"), "c5": (4096, 320, 240, "small")}[a.config]
     a.views = a.views or preset[0]
     a.width = a.width or preset[1]
     a.height = a.height or preset[2]
     a.map = a.map or preset[3]
     a.map_kw = {"water_prob": (1, 5)} if a.config == "c5" else {}
     a.rebuild = a.config == "c3"
+    a.models = 64 if a.config == "c4" else 0
+    a.sprites = 32 if a.config == "c5" else 0
     a.cvars = {"sw_maxsurfs": 40000, "sw_maxedges": 160000} if a.config == "c3" else {}
     return a
 
@@ -82,10 +84,28 @@ def advance_styles(r, step):
     r.run_lightstyles()
 
 
+def populate(args, scene, r, m):
+    """the entities of the config, the same on every rank and in every ref_soft process (the scene is replicated)"""
+    if args.models:
+        r.set_time(1.0)
+        scene.add_studio_models(r, m.cameras, args.models)
+    if args.sprites:
+        scene.add_sprites(r, m.cameras, args.sprites)
+
+
+def advance(args, r, step):
+    """what changes between two steps: c3 = the light styles, c4 = the client time the models animate on (new bones per step)"""
+    if args.rebuild:
+        advance_styles(r, step)
+    elif args.models:
+        r.set_time(1.0 + step / 60.0)
+
+
 def workload(args, world):
     what = {"c2": "static lightmaps (BASELINE.json configs[1])",
             "c3": "light styles 1..11 change every step: every surface-cache block that lists one is rebuilt per step (BASELINE.json configs[2])",
-            "c5": "turbulent water on ~10 % of the floor (BASELINE.json configs[4], per GPU)"}[args.config]
+            "c4": "static lightmaps + 64 skinned MDL v10 studio models (32 bones, 1536 vertices, 2976 triangles each), animated: new bones every step (BASELINE.json configs[3])",
+            "c5": "turbulent water on ~10 % of the floor + 32 translucent sprites sorted per view (BASELINE.json configs[4], per GPU)"}[args.config]
     mapname = {"small": "S (~1.7k faces; with pools ~2.2k)", "large": "L (~33k faces)", "medium": "M (~12.5k faces)", "tiny": "tiny"}[args.map]
     return {
         "workload": f"{args.config}: {args.views} batched camera views/GPU at {args.width}x{args.height}, synthetic BSP30 Map {mapname}, {what}",
@@ -170,14 +190,15 @@ def _soft_worker(conn, args_d, lo, hi, ncams):
         m = scene.make_map(args_d["map"], ncameras=ncams, **args_d["map_kw"])
         r = scene.Renderer(pkg.REF_SOFT_PATH, args_d["width"], args_d["height"], m, cvars=args_d["cvars"])
         cams = m.cameras[lo:hi]
+        ns = argparse.Namespace(**args_d)
+        populate(ns, scene, r, m)
         out = (np.empty((len(cams), args_d["height"], args_d["width"]), np.uint16), np.empty((len(cams), args_d["height"], args_d["width"]), np.int16))
         conn.send("ready")
         while True:
             cmd = conn.recv()
             if cmd == "quit":
                 break
-            if args_d["rebuild"]:
-                advance_styles(r, cmd[1])
+            advance(ns, r, cmd[1])
             t0 = time.perf_counter()
             r.render_views(cams, out=out)
             conn.send((time.perf_counter() - t0, r.last_seconds))
@@ -197,7 +218,7 @@ class SoftPool:
         for i in range(self.n):
             a, b = ctx.Pipe()
             d = {"map": args.map, "width": args.width, "height": args.height, "cpu": cpus[i % len(cpus)], "map_kw": args.map_kw,
-                 "cvars": args.cvars, "rebuild": args.rebuild}
+                 "cvars": args.cvars, "rebuild": args.rebuild, "models": args.models, "sprites": args.sprites}
             p = ctx.Process(target=_soft_worker, args=(b, d, int(bounds[i]), int(bounds[i + 1]), args.views), daemon=True)
             p.start()
             self.procs.append((p, a))
@@ -264,13 +285,13 @@ def cpu_baseline_one_core(args):
     scene = importlib.import_module("xash3d-fwgs_b200.scene")
     m = scene.make_map(args.map, ncameras=args.views, **args.map_kw)
     r = scene.Renderer(pkg.REF_SOFT_PATH, args.width, args.height, m, cvars=args.cvars)
+    populate(args, scene, r, m)
     cams = m.cameras[: min(args.views, 256)]
     out = (np.empty((len(cams), args.height, args.width), np.uint16), np.empty((len(cams), args.height, args.width), np.int16))
     r.render_views(cams, out=out)  # warm: fills the surface cache
     secs, passes, t0 = 0.0, 0, time.perf_counter()
     while time.perf_counter() - t0 < args.cpu_seconds and passes < 1000:
-        if args.rebuild:
-            advance_styles(r, passes + 1)
+        advance(args, r, passes + 1)
         r.render_views(cams, out=out)
         secs += r.last_seconds
         passes += 1
@@ -314,8 +335,8 @@ def run_cuda(args):
     lo, hi = shard.view_range(args.views * world, rank, world)  # this rank's slice of the global camera list
     cams = m.cameras[lo:hi]
     r = scene.Renderer(pkg.REF_CUDA_PATH, args.width, args.height, m, cvars={"cu_device": local})
-    if args.rebuild:
-        advance_styles(r, 0)
+    populate(args, scene, r, m)
+    advance(args, r, 0)
     n, w, h = len(cams), args.width, args.height
     px = n * w * h
 
@@ -339,6 +360,7 @@ def run_cuda(args):
     barrier()
     ms_step = allmax(ms)
     ms_scan = allmax(stages[4])
+    allmax_entities = allmax(stages[5])
 
     # -- second HBM-bound stage: every surface-cache block the batch samples rebuilt (config C3's
     #    behaviour under animated light styles), same batch, outside the headline timing
@@ -360,14 +382,12 @@ def run_cuda(args):
     # -- e2e: the public C-ABI call with host buffers (H2D view descriptors, D2H colour frames), wall clock
     def e2e_leg(zptr):
         for k in range(max(args.warmup, 3)):
-            if args.rebuild:
-                advance_styles(r, k + 1)
+            advance(args, r, k + 1)
             r.render_prepared(vp, pin.data_ptr(), zptr)
         barrier()
         t0 = time.perf_counter()
         for k in range(args.steps):
-            if args.rebuild:
-                advance_styles(r, k + 100)
+            advance(args, r, k + 100)
             r.render_prepared(vp, pin.data_ptr(), zptr)
         torch.cuda.synchronize()
         secs = allmax((time.perf_counter() - t0) / args.steps)
@@ -395,7 +415,7 @@ def run_cuda(args):
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "int32/f32 (16-bit pixel_t)", "data": "synthetic", "config": workload(args, world),
             "frames_per_s": n * world / (ms_step * 1e-3),
-            "stage_ms": {"vis_walk": stages[0], "faces_edges": stages[1], "surface_cache": stages[2], "spans": stages[3], "draw": stages[4],
+            "stage_ms": {"vis_walk": stages[0], "faces_edges": stages[1], "surface_cache": stages[2], "spans": stages[3], "draw": stages[4], "entities": stages[5],
                          "note": "the surface-cache kernels run on a side stream beside span generation: their time overlaps spans and is not part of the sum"},
             "e2e": {"value": total_px / e2e_s / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": px * 2 + 512,
                     "ms_per_step": e2e_s * 1e3,
@@ -417,6 +437,18 @@ def run_cuda(args):
                                       "kernel_ms": ms_blit, "traffic": None, "note": "2 B pixel_t read + 4 B display pixel written; 256 KB screen map in L2; not part of value / e2e"},
             "clocks": clocks, "counters": counters, "device": r.device_name(),
         }
+        if (args.models or args.sprites) and stages[5] > 0:
+            # per tested fragment 2 B of z read; per written fragment z + colour written and a skin texel read (6 B)
+            ent_bytes = 2 * counters["tri_pixels"] + 6 * max(counters["tri_written"], 0)
+            ent_ms = allmax_entities
+            line["roofline_entities"] = {
+                "bound": "hbm", "kernel": "k_studio_points + k_tris_fast + k_tris_fast_big + k_tri_resolve (opaque run) / k_item_order + k_tri_polys + k_tris_ordered (sorted run)",
+                "achieved": ent_bytes / world / (ent_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s", "frac": ent_bytes / world / (ent_ms * 1e-3) / 1e9 / peak,
+                "algorithmic_bytes_per_launch": ent_bytes // world, "kernel_ms": ent_ms, "traffic": None,
+                "triangles_set_up_per_s": counters["tris"] / world / (ent_ms * 1e-3), "fragments_tested_per_s": counters["tri_pixels"] / world / (ent_ms * 1e-3),
+                "submitted_triangle_view_pairs_per_s": (args.models * 2976 * n) / (ent_ms * 1e-3) if args.models else None,
+                "note": "the triangle stage is set-up- and atomic-bound, not HBM-bound: 2 B per z-tested fragment + 6 B per fragment that ends up visible "
+                        "(k_tri_resolve shades each pixel once; the reference writes every fragment that passes at its turn)"}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_one_core(args)
         print(json.dumps(line), flush=True)

@@ -50,8 +50,8 @@ REF_CUDA_EXPORT int RefCuda_BlitViews( int first, int nviews, void *dst, unsigne
 	unsigned int rmask, unsigned int gmask, unsigned int bmask, float *ms_kernel );
 
 /* Re-run the device stages of the last batch with all inputs resident in HBM; CUDA-event milliseconds
- * per iteration: total and per stage, ms_stage[5] = [visibility+BSP walk, face/edge set-up, surface cache,
- * span generation, span drawing].
+ * per iteration: total and per stage, ms_stage[6] = [visibility+BSP walk, face/edge set-up, surface cache,
+ * span generation, span drawing, entities (studio skinning + triangle rasteriser)].
  * flags: 1 = invalidate the surface cache before every iteration, 2 = flush L2 (256 MB write) between
  * iterations, outside the timed region, 8 = run the surface-cache kernels on the batch's stream instead of beside span
  * generation (times them alone; by default ms_stage[2] overlaps ms_stage[3]). */

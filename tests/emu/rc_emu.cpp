@@ -173,6 +173,13 @@ int rc_dev_set_studio( const rc_spart_t *parts, int nparts, const float *bones, 
 }
 
 /* one polygon fan of the triangle rasteriser, scanline by scanline (what the kernels do per row / per pixel) */
+/* RC_EMU_FASTKEYS=1: the leading opaque run is drawn the way k_tris_fast / k_tri_resolve do (rc_k_tris.cuh): a per-pixel
+ * maximum of (z << 32 | submission number), then every pixel shaded from the triangle its key names */
+struct emu_keyed_t { rc_trisetup_t ts; const rc_item_t *it; };
+static std::vector<unsigned long long> K_keys;
+static std::vector<emu_keyed_t> K_tris;
+static bool K_active = false;
+
 static void emu_draw_poly( const rc_item_t *it, const rc_fv_t *poly, int k, uint16_t *color, int16_t *zb, int width )
 {
 	rc_blendluts_t L = { E.colormap.data(), E.alphamap.data(), E.addmap.data(), E.modmap.data() };
@@ -185,6 +192,27 @@ static void emu_draw_poly( const rc_item_t *it, const rc_fv_t *poly, int k, uint
 		E.counters[RC_CTR_TRIS]++;
 		int32_t y0;
 		const int32_t nrows = rc_tri_rows( &ts, &y0 );
+		if( K_active )
+		{
+			K_tris.push_back( { ts, it } );
+			const unsigned long long id = K_tris.size();
+			for( int32_t r = 0; r < nrows; r++ )
+			{
+				rc_trirow_t row;
+				rc_tri_row( &ts, r, &row );
+				if( row.count <= 0 || !rc_tri_row_inbounds( &ts, &row ))
+					continue;
+				for( int32_t p = 0; p < row.count; p++ )
+				{
+					const size_t px = (size_t)( y0 + r ) * width + row.x + p;
+					const int32_t zi = (int32_t)((uint32_t)row.zi + (uint32_t)p * (uint32_t)ts.zistepx );
+					const unsigned long long key = ((unsigned long long)(uint32_t)(( zi >> 16 ) + 32768 ) << 32 ) | id;
+					if( key > K_keys[px] ) K_keys[px] = key;
+					E.counters[RC_CTR_TRI_PIXELS]++;
+				}
+			}
+			continue;
+		}
 		for( int32_t r = 0; r < nrows; r++ )
 		{
 			rc_trirow_t row;
@@ -204,7 +232,29 @@ static void emu_draw_poly( const rc_item_t *it, const rc_fv_t *poly, int k, uint
 	}
 }
 
-static void emu_draw_items( const rc_view_t *vw, uint16_t *color, int16_t *zb, int width )
+static void emu_keys_resolve( uint16_t *color, int16_t *zb, int width, int height )
+{
+	for( int y = 0; y < height; y++ )
+		for( int x = 0; x < width; x++ )
+		{
+			const size_t px = (size_t)y * width + x;
+			const uint32_t id = (uint32_t)K_keys[px];
+			if( !id ) continue;
+			const emu_keyed_t &kt = K_tris[id - 1];
+			int32_t y0;
+			rc_tri_rows( &kt.ts, &y0 );
+			rc_trirow_t row;
+			rc_tri_row( &kt.ts, y - y0, &row );
+			const int32_t p = x - row.x;
+			const uint32_t src = E.texels[kt.it->tex_ofs + rc_tri_texel( &kt.ts, &row, p )];
+			const uint32_t light = (uint32_t)row.l + (uint32_t)p * (uint32_t)kt.ts.lstepx;
+			color[px] = (uint16_t)( E.colormap[( src >> 3 ) | (( light & 0x1F00u ) << 5 )] | ( src & 7 ));
+			zb[px] = (int16_t)( (int32_t)( K_keys[px] >> 32 ) - 32768 );
+		}
+	K_active = false;
+}
+
+static void emu_draw_items( const rc_view_t *vw, uint16_t *color, int16_t *zb, int width, int height )
 {
 	if( E.items.empty() || !color || !zb )
 		return;
@@ -231,8 +281,21 @@ static void emu_draw_items( const rc_view_t *vw, uint16_t *color, int16_t *zb, i
 		for( int e : ents )
 			for( int j = 0; j < E.sortents[e].nitems; j++ ) order.push_back( E.sortents[e].first_item + j );
 	}
+	int nfast = 0;
+	if( getenv( "RC_EMU_FASTKEYS" ))
+	{
+		int tris = 0;
+		for( size_t i = 0; i < E.items.size() && E.items[i].drawer == RC_DRAW_FILL && E.items[i].sortent < 0; i++ ) { nfast++; tris += E.items[i].count; }
+		if( tris < 64 ) nfast = 0;
+	}
+	if( nfast )
+	{
+		K_keys.resize( (size_t)width * height ); K_tris.clear(); K_active = true;
+		for( size_t i = 0; i < K_keys.size(); i++ ) K_keys[i] = (unsigned long long)(uint32_t)( (int32_t)zb[i] + 32768 ) << 32;
+	}
 	for( int idx : order )
 	{
+		if( K_active && idx >= nfast ) emu_keys_resolve( color, zb, width, height );
 		const rc_item_t *it = &E.items[idx];
 		if( it->tex_ofs < 0 ) continue;
 		rc_fv_t poly[8];
@@ -272,6 +335,7 @@ static void emu_draw_items( const rc_view_t *vw, uint16_t *color, int16_t *zb, i
 			}
 		}
 	}
+	if( K_active ) emu_keys_resolve( color, zb, width, height );
 }
 
 int rc_dev_set_lightstyles( const int32_t *values ) { memcpy( E.styles, values, sizeof( E.styles )); return 0; }
@@ -422,7 +486,7 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 				}
 			}
 		}
-		emu_draw_items( vw, color, zb, width );
+		emu_draw_items( vw, color, zb, width, height );
 		E.vsurfs[vi] = surfs; E.vedges[vi] = edges;
 		E.counters[RC_CTR_VIEWS]++; E.counters[RC_CTR_PIXELS] += (uint64_t)vw_w * vw_h;
 	}
@@ -439,7 +503,7 @@ int rc_dev_blit( int, int, void *, size_t, float * ) { snprintf( E.err, sizeof( 
 int rc_dev_bench_resident( int, int, float *ms_total, float *ms_stage )
 {
 	if( ms_total ) *ms_total = 0;
-	if( ms_stage ) memset( ms_stage, 0, 4 * sizeof( float ));
+	if( ms_stage ) memset( ms_stage, 0, RC_BENCH_STAGES * sizeof( float ));
 	return -1;
 }
 

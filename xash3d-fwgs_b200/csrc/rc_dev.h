@@ -51,13 +51,13 @@ int rc_dev_flush_cache( void );
 int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, int clear, uint16_t *color_out, int16_t *z_out );
 
 /* re-run the device stages of the last rc_dev_render batch (inputs resident in HBM) 'iters' times and
- * report CUDA-event milliseconds: total and per stage (vis+walk, faces, cache, spans, draw).  The cache kernels run
+ * report CUDA-event milliseconds: total and per stage (vis+walk, faces, cache, spans, draw, entities).  The cache kernels run
  * on a side stream beside span generation: their time (own events) is not part of the sum of the other stages */
 #define RC_BENCH_REBUILD_CACHE 1 /* invalidate every cache block before each iteration (config C3 behaviour) */
 #define RC_BENCH_FLUSH_L2      2 /* write 256 MB between iterations, outside the timed region */
 #define RC_BENCH_OVERLAP       4 /* run the batch as rc_dev_render does for host outputs: 4 view slices on 2 streams (total only) */
 #define RC_BENCH_SERIAL_CACHE  8 /* surface-cache kernels on the batch's own stream instead of beside span generation: times them alone */
-#define RC_BENCH_STAGES        5 /* vis+walk, faces, cache, spans, draw */
+#define RC_BENCH_STAGES        6 /* vis+walk, faces, cache, spans, draw, entities */
 int rc_dev_bench_resident( int iters, int flags, float *ms_total, float *ms_stage /* [RC_BENCH_STAGES] */ );
 
 /* display tail (R_BuildScreenMap / R_BlitScreen, ref/soft/r_glblit.c:347,591): table[65536] maps pixel_t to the

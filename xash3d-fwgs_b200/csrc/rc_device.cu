@@ -88,6 +88,11 @@ struct rc_work_t
 	int32_t   *item_order;  /* [nviews][nitems] */
 	struct rc_poly_t *polys; /* [nviews][ntris] */
 	const uint16_t *alphamap; const uint8_t *addmap, *modmap;
+	int32_t    nfast_items, fast_tris;  /* the leading run of opaque items: k_tris_fast instead of k_tris_ordered */
+	unsigned long long *trikeys;        /* [nviews][height][width] z << 32 | triangle number */
+	int32_t   *big_list, *big_count; int32_t big_cap; /* triangles k_tris_fast hands to k_tris_fast_big: {view, key number} */
+	/* studio models (k_studio_points) */
+	const uint8_t *sstatic; const rc_spart_t *parts; const float *bones, *blight; float *mvpos; int32_t *mlight;
 };
 
 #define SP_LINES 32 /* scanlines per band (rc_k_spans.cuh): k_faces bins edges by band */
@@ -563,7 +568,7 @@ struct Dev
 	cudaStream_t aux_stream[RC_MAX_SLICES] = {};           /* surface-cache kernels of a slice, beside its span kernels */
 	cudaEvent_t ev_cache[RC_MAX_SLICES][2] = {};           /* start / end of those */
 	bool cache_aside = true;                               /* false: on the slice's own stream (the bench times the kernels alone) */
-	cudaEvent_t ev[8] = {};
+	cudaEvent_t ev[10] = {};
 	uint64_t launches = 0, h2d_bytes = 0;
 	bool sync_each = false; /* RC_SYNC_EACH in the environment: synchronise and check after every kernel (names the one that faults) */
 
@@ -606,6 +611,9 @@ struct Dev
 	int nitems = 0, ncorners = 0, nsortents = 0;
 	std::vector<rc_item_t> h_items;
 	int ntris = 0;                       /* triangles of the items */
+	int nfast_items = 0, fast_tris = 0;  /* leading opaque run */
+	unsigned long long *d_trikeys = nullptr; size_t cap_trikeys = 0;
+	int32_t *d_biglist = nullptr; size_t cap_big = 0;
 	int32_t *d_item_order = nullptr; rc_poly_t *d_polys = nullptr;
 	size_t cap_item_order = 0, cap_polys = 0;
 
@@ -826,9 +834,27 @@ rc_work_t make_slice( int k, int v0, int v1 )
 	ws.dlights = D.d_dlights; ws.dlightbits = D.d_dlightbits; ws.ndlights = D.ndlights;
 	ws.items = D.d_items; ws.corners = D.d_corners; ws.sortents = D.d_sortents; ws.nitems = D.nitems; ws.nsortents = D.nsortents;
 	ws.item_order = D.d_item_order ? D.d_item_order + (size_t)v0 * D.nitems : nullptr;
-	ws.polys = D.d_polys ? D.d_polys + (size_t)v0 * D.ntris : nullptr;
 	ws.alphamap = D.d_alphamap; ws.addmap = D.d_addmap; ws.modmap = D.d_modmap;
+	ws.polys = D.d_polys ? D.d_polys + (size_t)v0 * ( D.ntris - D.fast_tris ) : nullptr;
+	ws.nfast_items = D.nfast_items; ws.fast_tris = D.fast_tris;
+	ws.trikeys = D.d_trikeys ? D.d_trikeys + (size_t)v0 * ws.width * ws.height : nullptr;
+	ws.big_cap = (int32_t)( D.cap_big / RC_MAX_SLICES ); ws.big_list = D.d_biglist ? D.d_biglist + (size_t)2 * ws.big_cap * k : nullptr;
+	ws.big_count = D.d_nlist + 8 * k + 3; /* line_cursor[1] is free again once k_lines is done */
+	ws.sstatic = D.d_sstatic; ws.parts = D.d_parts; ws.bones = D.d_bones; ws.blight = D.d_blight; ws.mvpos = D.d_mvpos; ws.mlight = D.d_mlight;
 	return ws;
+}
+
+/* the studio models' vertices and light levels do not depend on the view: once per batch */
+int launch_studio_points( cudaStream_t st )
+{
+	if( !D.nparts || !D.nitems || !D.studio_dirty )
+		return 0;
+	const rc_work_t ws = make_slice( 0, 0, D.w.nviews );
+	const int np = D.totalverts + D.totalnorms;
+	k_studio_points<<<( np + 255 ) / 256, 256, 0, st>>>( D.sc, ws, D.nparts, D.totalverts, D.totalnorms ); D.launches++;
+	KCHECK( "k_studio_points", st );
+	D.studio_dirty = false;
+	return 0;
 }
 
 /* all stages of one slice on stream st; evs != NULL: stage boundaries are recorded there */
@@ -885,18 +911,36 @@ int launch_slice( const rc_work_t &ws, int k, cudaStream_t st, cudaEvent_t *evs,
 		k_draw<<<dblocks < DR_GRID ? dblocks : DR_GRID, DR_WARPS * 32, rc_draw_smem( ws.width, lpw ), st>>>( sc, ws, 0, nlines, lpw );
 		D.launches++;
 		KCHECK( "k_draw", st );
+		if( evs ) CK( cudaEventRecord( evs[5], st ));
 		if( D.nitems && D.ntris )
 		{
 			/* entities: after the world's spans are in the frame (R_DrawEntitiesOnList follows R_EdgeDrawing, r_main.c:1090) */
-			k_item_order<<<ws.nviews, 128, 0, st>>>( ws ); D.launches++;
-			dim3 gp(( D.ntris + 127 ) / 128, ws.nviews );
-			k_tri_polys<<<gp, 128, 0, st>>>( ws, D.ntris ); D.launches++;
-			dim3 gt( ws.nviews, TR_STRIPS );
-			k_tris_ordered<<<gt, TR_THREADS, 0, st>>>( sc, ws, D.ntris ); D.launches++;
+			if( launch_studio_points( st ) != 0 ) return -1;
+			if( D.fast_tris )
+			{
+				CK( cudaMemsetAsync( ws.big_count, 0, sizeof( int32_t ), st ));
+				k_tri_keys_init<<<D.num_sms * 8, 256, 0, st>>>( ws ); D.launches++;
+				dim3 gf(( D.fast_tris + 127 ) / 128, ws.nviews );
+				k_tris_fast<<<gf, 128, 0, st>>>( ws ); D.launches++;
+				KCHECK( "k_tris_fast", st );
+				k_tris_fast_big<<<D.num_sms * 8, 128, 0, st>>>( ws ); D.launches++;
+				k_tri_resolve<<<D.num_sms * 16, 128, 0, st>>>( sc, ws ); D.launches++;
+				KCHECK( "k_tri_resolve", st );
+			}
+			const int nord = D.ntris - D.fast_tris;
+			if( nord > 0 )
+			{
+				k_item_order<<<ws.nviews, 128, 0, st>>>( ws ); D.launches++;
+				dim3 gp(( nord + 127 ) / 128, ws.nviews );
+				k_tri_polys<<<gp, 128, 0, st>>>( ws, nord ); D.launches++;
+				dim3 gt( ws.nviews, TR_STRIPS );
+				k_tris_ordered<<<gt, TR_THREADS, 0, st>>>( sc, ws, nord ); D.launches++;
+			}
 			KCHECK( "k_tris", st );
 		}
 	}
-	if( evs ) CK( cudaEventRecord( evs[5], st ));
+	else if( evs ) CK( cudaEventRecord( evs[5], st ));
+	if( evs ) CK( cudaEventRecord( evs[6], st ));
 	return 0;
 }
 
@@ -911,6 +955,7 @@ int run_batch( int nslices, int nstreams, bool timed, uint16_t *color_out, int16
 	cudaStream_t st = D.stream;
 	const size_t vpx = (size_t)w.width * w.height;
 	CK( cudaMemsetAsync( D.d_counters, 0, sizeof( unsigned long long ) * RC_CTR_COUNT, st ));
+	if( nslices > 1 && launch_studio_points( st ) != 0 ) return -1; /* ahead of the fork: every slice reads the result */
 	if( nslices <= 1 )
 	{
 		const rc_work_t ws = make_slice( 0, 0, w.nviews );
@@ -992,7 +1037,7 @@ void rc_dev_shutdown( void )
 	cudaDeviceSynchronize();
 	free_batch();
 	/* everything rc_dev_init / the uploads created, so that R_Shutdown + R_Init (vid_restart) starts clean */
-	void **ptrs[] = { (void **)&D.d_sstatic, (void **)&D.d_parts, (void **)&D.d_bones, (void **)&D.d_blight, (void **)&D.d_mvpos, (void **)&D.d_mlight, (void **)&D.d_item_order, (void **)&D.d_polys, (void **)&D.d_alphamap, (void **)&D.d_addmap, (void **)&D.d_modmap, (void **)&D.d_items, (void **)&D.d_corners, (void **)&D.d_sortents, (void **)&D.d_display, (void **)&D.d_screenmap, (void **)&D.d_dlights, (void **)&D.d_dlightbits,
+	void **ptrs[] = { (void **)&D.d_trikeys, (void **)&D.d_biglist, (void **)&D.d_sstatic, (void **)&D.d_parts, (void **)&D.d_bones, (void **)&D.d_blight, (void **)&D.d_mvpos, (void **)&D.d_mlight, (void **)&D.d_item_order, (void **)&D.d_polys, (void **)&D.d_alphamap, (void **)&D.d_addmap, (void **)&D.d_modmap, (void **)&D.d_items, (void **)&D.d_corners, (void **)&D.d_sortents, (void **)&D.d_display, (void **)&D.d_screenmap, (void **)&D.d_dlights, (void **)&D.d_dlightbits,
 		(void **)&D.d_colormap, (void **)&D.d_lightgamma, (void **)&D.d_sintable, (void **)&D.d_textures, (void **)&D.d_texels,
 		(void **)&D.d_styles, (void **)&D.d_keys, (void **)&D.d_need, (void **)&D.d_list, (void **)&D.d_nlist,
 		(void **)&D.d_counters, &D.d_flush };
@@ -1002,6 +1047,7 @@ void rc_dev_shutdown( void )
 	D.cap_cands = D.cap_edges = D.cap_blk_events = 0; D.caps_dirty = false;
 	D.nitems = D.ncorners = D.nsortents = 0; D.h_items.clear(); D.ntris = 0; D.cap_item_order = D.cap_polys = 0;
 	D.nparts = D.totalverts = D.totalnorms = 0; D.cap_mvpos = D.cap_mlight = 0; D.studio_dirty = false;
+	D.nfast_items = D.fast_tris = 0; D.cap_trikeys = D.cap_big = 0;
 	D.display_bytes = 0; D.ndlights = 0; D.screen_bpp = 0; D.cache_texels = 0; D.ntextures = 0;
 	D.sc = rc_scene_t{}; D.h_surfaces.clear(); D.h_textures.clear();
 	cudaStream_t *streams[] = { &D.stream, &D.copy };
@@ -1153,6 +1199,10 @@ int rc_dev_set_items( const rc_item_t *items, int nitems, const rc_corner_t *cor
 	D.h_items.assign( items, items + nitems );
 	D.ntris = 0;
 	for( int i = 0; i < nitems; i++ ) D.ntris += items[i].count;
+	/* the leading run of opaque, fixed-order items takes the order-free path when it is worth its key buffer */
+	D.nfast_items = D.fast_tris = 0;
+	for( int i = 0; i < nitems && items[i].drawer == RC_DRAW_FILL && items[i].sortent < 0; i++ ) { D.nfast_items++; D.fast_tris += items[i].count; }
+	if( D.fast_tris < 64 ) D.nfast_items = D.fast_tris = 0;
 	D.h2d_bytes += sizeof( rc_item_t ) * (size_t)nitems + sizeof( rc_corner_t ) * (size_t)ncorners + sizeof( rc_sortent_t ) * (size_t)nsortents;
 	return 0;
 }
@@ -1241,7 +1291,13 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 		if( ensure_batch( nviews, width, height ) != 0 ) return -1;
 		if( D.nitems && D.ntris )
 		{
-			const size_t need_o = (size_t)D.cap_views * D.nitems, need_p = (size_t)D.cap_views * D.ntris;
+			const size_t need_o = (size_t)D.cap_views * D.nitems, need_p = (size_t)D.cap_views * ( D.ntris - D.fast_tris ) + 1;
+			if( D.fast_tris )
+			{
+				const size_t need_k = (size_t)D.cap_views * width * height, need_b = (size_t)RC_MAX_SLICES * ( (size_t)D.cap_views * 4096 + 65536 );
+				if( need_k > D.cap_trikeys ) { if( dalloc( &D.d_trikeys, need_k ) != 0 ) return -1; D.cap_trikeys = need_k; }
+				if( need_b > D.cap_big ) { if( dalloc( &D.d_biglist, 2 * need_b ) != 0 ) return -1; D.cap_big = need_b; }
+			}
 			if( need_o > D.cap_item_order ) { if( dalloc( &D.d_item_order, need_o ) != 0 ) return -1; D.cap_item_order = need_o; }
 			if( need_p > D.cap_polys ) { if( dalloc( &D.d_polys, need_p ) != 0 ) return -1; D.cap_polys = need_p; }
 		}
@@ -1296,6 +1352,7 @@ int rc_dev_bench_resident( int iters, int flags, float *ms_total, float *ms_stag
 	{
 		if( flags & RC_BENCH_FLUSH_L2 ) /* untimed: the events bracket the stages only */
 			CK( cudaMemsetAsync( D.d_flush, it & 0xFF, flush_bytes, D.stream ));
+		if( D.nparts ) D.studio_dirty = true; /* skinning is per-frame work (R_StudioDrawPoints): part of every iteration */
 		if( flags & RC_BENCH_REBUILD_CACHE )
 			CK( cudaMemsetAsync( D.d_keys, 0, sizeof( rc_cachekey_t ) * (size_t)D.sc.numsurfaces * 4, D.stream ));
 		{
@@ -1365,11 +1422,11 @@ int rc_dev_blit( int first, int nviews, void *dst, size_t stride, float *ms_kern
 	const uint16_t *src = D.w.color + fpx * first;
 	const size_t want = ( npx / 8 + 255 ) / 256;
 	const int grid = (int)( want < 148 * 8 ? ( want ? want : 1 ) : 148 * 8 );
-	if( ms_kernel ) CK( cudaEventRecord( D.ev[6], D.stream ));
+	if( ms_kernel ) CK( cudaEventRecord( D.ev[8], D.stream ));
 	if( D.screen_bpp == 2 ) k_blit<2><<<grid, 256, 0, D.stream>>>( src, D.d_screenmap, D.d_display, npx );
 	else k_blit<4><<<grid, 256, 0, D.stream>>>( src, D.d_screenmap, D.d_display, npx );
 	D.launches++;
-	if( ms_kernel ) CK( cudaEventRecord( D.ev[7], D.stream ));
+	if( ms_kernel ) CK( cudaEventRecord( D.ev[9], D.stream ));
 	CK( cudaGetLastError());
 	if( dst )
 	{
@@ -1378,7 +1435,7 @@ int rc_dev_blit( int first, int nviews, void *dst, size_t stride, float *ms_kern
 		CK( cudaMemcpy2DAsync( dst, stride * D.screen_bpp, D.d_display, rowbytes, rowbytes, (size_t)D.w.height * nviews, cudaMemcpyDeviceToHost, D.stream ));
 	}
 	CK( cudaStreamSynchronize( D.stream ));
-	if( ms_kernel ) CK( cudaEventElapsedTime( ms_kernel, D.ev[6], D.ev[7] ));
+	if( ms_kernel ) CK( cudaEventElapsedTime( ms_kernel, D.ev[8], D.ev[9] ));
 	return 0;
 }
 

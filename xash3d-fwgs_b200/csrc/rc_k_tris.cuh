@@ -86,27 +86,83 @@ __device__ __forceinline__ int rc_item_corners( const rc_work_t &w, const rc_vie
 		c[2] = tri ? q[3] : q[2];
 		return 1;
 	}
+	if( it->kind == RC_ITEM_MESH )
+	{
+		/* a studio mesh: static strip corners, the entity's transformed vertices and per-normal lights (k_studio_points) */
+		const rc_mcorner_t *mc = reinterpret_cast<const rc_mcorner_t *>( w.sstatic ) + it->first + 3 * tri;
+#pragma unroll
+		for( int q = 0; q < 3; q++ )
+		{
+			const rc_mcorner_t m = mc[q];
+			const float *p = w.mvpos + (size_t)( it->vert_base + m.vert ) * 3;
+			c[q].xyz[0] = p[0]; c[q].xyz[1] = p[1]; c[q].xyz[2] = p[2];
+			c[q].l = w.mlight[it->light_base + m.norm]; c[q].s = m.s; c[q].t = m.t;
+		}
+		return 1;
+	}
 	const rc_corner_t *src = w.corners + it->first + 3 * tri;
 	c[0] = src[0]; c[1] = src[1]; c[2] = src[2];
 	return 1;
 }
 
-__global__ void __launch_bounds__( 128 ) k_tri_polys( rc_work_t w, int32_t ntris )
+/* the item a triangle number belongs to: items are few, their order0 ascending */
+__device__ __forceinline__ const rc_item_t *rc_item_of( const rc_work_t &w, int32_t g )
 {
-	const int view = blockIdx.y;
-	const int32_t g = blockIdx.x * blockDim.x + threadIdx.x;
-	if( g >= ntris )
-		return;
-	/* the item this triangle belongs to: items are few, their order0 ascending */
 	int32_t lo = 0, hi = w.nitems - 1;
 	while( lo < hi )
 	{
 		const int32_t mid = ( lo + hi + 1 ) >> 1;
 		if( w.items[mid].order0 <= g ) lo = mid; else hi = mid - 1;
 	}
-	const rc_item_t *it = &w.items[lo];
+	return &w.items[lo];
+}
+
+/* R_StudioDrawPoints' vertex and normal loops (r_studio.c:1846-1895) for every drawn (entity, submodel) of the batch, once
+ * per batch (they do not depend on the view): thread per vertex, then thread per normal */
+__global__ void __launch_bounds__( 256 ) k_studio_points( rc_scene_t sc, rc_work_t w, int32_t nparts, int32_t totalverts, int32_t totalnorms )
+{
+	const int32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+	if( g >= totalverts + totalnorms )
+		return;
+	const bool isnorm = g >= totalverts;
+	const int32_t idx = isnorm ? g - totalverts : g;
+	/* the part whose slice holds idx */
+	int32_t lo = 0, hi = nparts - 1;
+	while( lo < hi )
+	{
+		const int32_t mid = ( lo + hi + 1 ) >> 1;
+		if(( isnorm ? w.parts[mid].light_base : w.parts[mid].vert_base ) <= idx ) lo = mid; else hi = mid - 1;
+	}
+	const rc_spart_t pt = w.parts[lo];
+	const float *sf = reinterpret_cast<const float *>( w.sstatic );
+	if( !isnorm )
+	{
+		const int32_t i = idx - pt.vert_base;
+		if( i >= pt.numverts ) return;
+		float out[3];
+		rc_studio_vertex( w.bones + (size_t)( pt.bones + w.sstatic[pt.svertbone + i] ) * 12, sf + pt.sverts + 3 * i, out );
+		float *dst = w.mvpos + (size_t)idx * 3;
+		dst[0] = out[0]; dst[1] = out[1]; dst[2] = out[2];
+	}
+	else
+	{
+		const int32_t k = idx - pt.light_base;
+		if( k >= pt.numnorms ) return;
+		w.mlight[idx] = rc_studio_light( &pt, w.sstatic[pt.snormflags + k], sf + pt.snorms + 3 * k,
+			w.blight + (size_t)( pt.blightvec + w.sstatic[pt.snormbone + k] ) * 3, sc.lightgamma );
+	}
+}
+
+__global__ void __launch_bounds__( 128 ) k_tri_polys( rc_work_t w, int32_t ntris )
+{
+	const int view = blockIdx.y;
+	const int32_t gl = blockIdx.x * blockDim.x + threadIdx.x;
+	if( gl >= ntris )
+		return;
+	const int32_t g = gl + w.fast_tris; /* the triangles before fast_tris go through k_tris_fast */
+	const rc_item_t *it = rc_item_of( w, g );
 	const rc_view_t *vw = &w.views[view];
-	rc_poly_t *out = w.polys + (size_t)view * ntris + g;
+	rc_poly_t *out = w.polys + (size_t)view * ntris + gl;
 	rc_corner_t c[3];
 	rc_fv_t poly[8];
 	int k = 0;
@@ -140,14 +196,14 @@ __global__ void __launch_bounds__( TR_THREADS ) k_tris_ordered( rc_scene_t sc, r
 		if( idx < 0 )
 			break;
 		const rc_item_t *it = &w.items[idx];
-		if( it->tex_ofs < 0 )
+		if( it->tex_ofs < 0 || idx < w.nfast_items )
 			continue;
 		const uint16_t *skin = sc.texels + it->tex_ofs;
 		const int32_t drawer = it->drawer;
 		const uint32_t icolor = (uint32_t)it->color, ialpha = (uint32_t)it->alpha;
 		for( int32_t tri = 0; tri < it->count; tri++ )
 		{
-			const rc_poly_t *pl = &polys[it->order0 + tri];
+			const rc_poly_t *pl = &polys[it->order0 - w.fast_tris + tri];
 			const int32_t k = pl->k;
 			for( int32_t i = 1; i < k - 1; i++ )
 			{
@@ -195,6 +251,173 @@ __global__ void __launch_bounds__( TR_THREADS ) k_tris_ordered( rc_scene_t sc, r
 	}
 	if( lane == 0 && npix ) atomicAdd( &w.counters[RC_CTR_TRI_PIXELS], npix );
 	if( t == 0 && ndrawn ) atomicAdd( &w.counters[RC_CTR_TRIS], ndrawn );
+}
+
+/* ---------------------------------------------------------------------------------------------- */
+/*
+ * The opaque fast path.  R_PolysetFillSpans8 (r_polyse.c:1134) is "if( z >= *pz ) { *pz = z; *pdest = shade; }" applied
+ * triangle after triangle: the z a pixel ends with is the largest of the world's and every covering triangle's, and its
+ * colour is that of the LAST triangle in submission order that reaches that largest z (an equal z overwrites).  Both are
+ * the maximum of the 64-bit key (z << 32 | submission number): a run of opaque triangles needs no ordering at all -
+ *   k_tri_keys_init  key = the world's z, number 0
+ *   k_tris_fast      thread per (view, triangle): final verts, clip, edge walk; atomicMax of its key on every covered
+ *                    pixel (read first: most fragments of a hidden model lose without an atomic); triangles with many
+ *                    pixels are queued for k_tris_fast_big, a warp per triangle, lanes across the pixels of a scanline
+ *   k_tri_resolve    thread per pixel whose key carries a triangle number: that triangle is set up again and this one
+ *                    pixel shaded from it (texel, light level through the colour map), z from the key
+ * The host sends the leading run of opaque items down this path (C4: every studio model); whatever follows it goes
+ * through k_tris_ordered.
+ */
+#define TF_BIG_PIXELS 192
+
+__global__ void __launch_bounds__( 256 ) k_tri_keys_init( rc_work_t w )
+{
+	const size_t n = (size_t)w.nviews * w.width * w.height;
+	for( size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x )
+		w.trikeys[i] = (unsigned long long)(uint32_t)( (int32_t)w.zbuf[i] + 32768 ) << 32;
+}
+
+/* one scanline of a set-up triangle into the key buffer; lanes: p0 = first pixel this caller takes, pstep = stride */
+__device__ __forceinline__ uint32_t rc_fast_row( const rc_trisetup_t *ts, int32_t r, unsigned long long *krow, uint32_t id, int32_t p0, int32_t pstep )
+{
+	rc_trirow_t row;
+	rc_tri_row( ts, r, &row );
+	if( row.count <= 0 || !rc_tri_row_inbounds( ts, &row ))
+		return 0;
+	unsigned long long *kp = krow + row.x;
+	for( int32_t p = p0; p < row.count; p += pstep )
+	{
+		const int32_t zi = (int32_t)((uint32_t)row.zi + (uint32_t)p * (uint32_t)ts->zistepx );
+		const unsigned long long key = ((unsigned long long)(uint32_t)(( zi >> 16 ) + 32768 ) << 32 ) | id;
+		if( key > kp[p] )
+			atomicMax( &kp[p], key );
+	}
+	return (uint32_t)row.count;
+}
+
+__global__ void __launch_bounds__( 128 ) k_tris_fast( rc_work_t w )
+{
+	const int view = blockIdx.y;
+	const int32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+	unsigned long long npix = 0, ntri = 0;
+	if( g < w.fast_tris )
+	{
+		const rc_item_t *it = rc_item_of( w, g );
+		const rc_view_t *vw = &w.views[view];
+		rc_corner_t c[3];
+		rc_fv_t poly[8];
+		int k = 0;
+		if( it->tex_ofs >= 0 && g - it->order0 < it->count && rc_item_corners( w, vw, it, g - it->order0, c ))
+			k = rc_view_triangle( vw, &c[0], &c[1], &c[2], poly );
+		unsigned long long *keys = w.trikeys + (size_t)view * w.width * w.height;
+		for( int i = 1; i < k - 1; i++ )
+		{
+			rc_trisetup_t ts;
+			if( !rc_tri_setup( &poly[0], &poly[i], &poly[i + 1], it->skinwidth, it->skinheight, &ts ))
+				continue;
+			ntri++;
+			int32_t y0;
+			const int32_t rows = rc_tri_rows( &ts, &y0 );
+			const uint32_t id = (uint32_t)g * 8u + (uint32_t)i + 1u;
+			/* a rough pixel count: rows x the widest of the first, middle and last scanline */
+			rc_trirow_t ra, rb, rm;
+			rc_tri_row( &ts, 0, &ra ); rc_tri_row( &ts, rows - 1, &rb ); rc_tri_row( &ts, rows >> 1, &rm );
+			const int32_t wmax = max( max( ra.count, rb.count ), rm.count );
+			if( (long long)rows * wmax > TF_BIG_PIXELS )
+			{
+				const int32_t slot = atomicAdd( w.big_count, 1 );
+				if( slot < w.big_cap )
+				{
+					w.big_list[2 * slot] = view; w.big_list[2 * slot + 1] = (int32_t)id;
+					continue;
+				}
+			}
+			for( int32_t r = 0; r < rows; r++ )
+				npix += rc_fast_row( &ts, r, keys + (size_t)( y0 + r ) * w.width, id, 0, 1 );
+		}
+	}
+	/* counters: one atomic per warp */
+	const unsigned m = __activemask();
+	const unsigned np = __reduce_add_sync( m, (unsigned)npix ), nt = __reduce_add_sync( m, (unsigned)ntri );
+	if(( threadIdx.x & 31 ) == __ffs( (int)m ) - 1 )
+	{
+		if( np ) atomicAdd( &w.counters[RC_CTR_TRI_PIXELS], (unsigned long long)np );
+		if( nt ) atomicAdd( &w.counters[RC_CTR_TRIS], (unsigned long long)nt );
+	}
+}
+
+/* the set-up of fan triangle `fan` of triangle g for a view, again (k_tris_fast_big, k_tri_resolve); 0 = not drawn */
+__device__ __forceinline__ int rc_fast_setup( const rc_work_t &w, int view, int32_t g, int32_t fan, rc_trisetup_t *ts, const rc_item_t **pit )
+{
+	const rc_item_t *it = rc_item_of( w, g );
+	*pit = it;
+	rc_corner_t c[3];
+	rc_fv_t poly[8];
+	if( !rc_item_corners( w, &w.views[view], it, g - it->order0, c ))
+		return 0;
+	const int k = rc_view_triangle( &w.views[view], &c[0], &c[1], &c[2], poly );
+	if( fan < 1 || fan >= k - 1 )
+		return 0;
+	return rc_tri_setup( &poly[0], &poly[fan], &poly[fan + 1], it->skinwidth, it->skinheight, ts );
+}
+
+__global__ void __launch_bounds__( 128 ) k_tris_fast_big( rc_work_t w )
+{
+	const int lane = threadIdx.x & 31;
+	int32_t n = *w.big_count;
+	if( n > w.big_cap ) n = w.big_cap;
+	if( blockIdx.x == 0 && threadIdx.x == 0 && n ) atomicAdd( &w.counters[RC_CTR_BIG_TRIS], (unsigned long long)n );
+	const int32_t nwarps = gridDim.x * ( blockDim.x >> 5 );
+	unsigned long long npix = 0;
+	for( int32_t e = blockIdx.x * ( blockDim.x >> 5 ) + ( threadIdx.x >> 5 ); e < n; e += nwarps )
+	{
+		const int view = w.big_list[2 * e];
+		const uint32_t id = (uint32_t)w.big_list[2 * e + 1];
+		rc_trisetup_t ts;
+		const rc_item_t *it;
+		if( !rc_fast_setup( w, view, (int32_t)(( id - 1u ) >> 3 ), (int32_t)(( id - 1u ) & 7u ), &ts, &it ))
+			continue;
+		int32_t y0;
+		const int32_t rows = rc_tri_rows( &ts, &y0 );
+		unsigned long long *keys = w.trikeys + (size_t)view * w.width * w.height;
+		for( int32_t r = 0; r < rows; r++ )
+		{
+			const uint32_t cnt = rc_fast_row( &ts, r, keys + (size_t)( y0 + r ) * w.width, id, lane, 32 );
+			if( lane == 0 ) npix += cnt;
+		}
+	}
+	if( lane == 0 && npix ) atomicAdd( &w.counters[RC_CTR_TRI_PIXELS], npix );
+}
+
+__global__ void __launch_bounds__( 128 ) k_tri_resolve( rc_scene_t sc, rc_work_t w )
+{
+	const size_t vpx = (size_t)w.width * w.height, n = (size_t)w.nviews * vpx;
+	unsigned nw = 0;
+	for( size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x )
+	{
+		const unsigned long long key = w.trikeys[i];
+		const uint32_t id = (uint32_t)key;
+		if( !id )
+			continue;
+		const int view = (int)( i / vpx );
+		const int32_t pix = (int32_t)( i - (size_t)view * vpx ), y = pix / w.width, x = pix - y * w.width;
+		rc_trisetup_t ts;
+		const rc_item_t *it;
+		if( !rc_fast_setup( w, view, (int32_t)(( id - 1u ) >> 3 ), (int32_t)(( id - 1u ) & 7u ), &ts, &it ))
+			continue;
+		int32_t y0;
+		rc_tri_rows( &ts, &y0 );
+		rc_trirow_t row;
+		rc_tri_row( &ts, y - y0, &row );
+		const int32_t p = x - row.x;
+		const uint32_t src = __ldg( sc.texels + it->tex_ofs + rc_tri_texel( &ts, &row, p ));
+		const uint32_t light = (uint32_t)row.l + (uint32_t)p * (uint32_t)ts.lstepx;
+		w.color[i] = (uint16_t)( __ldg( sc.colormap + (( src >> 3 ) | (( light & 0x1F00u ) << 5 ))) | ( src & 7u ));
+		w.zbuf[i] = (int16_t)( (int32_t)( key >> 32 ) - 32768 );
+		nw++;
+	}
+	nw = __reduce_add_sync( 0xFFFFFFFFu, nw );
+	if(( threadIdx.x & 31 ) == 0 && nw ) atomicAdd( &w.counters[RC_CTR_TRI_WRITTEN], (unsigned long long)nw );
 }
 
 #endif /* RC_K_TRIS_CUH */

@@ -285,7 +285,8 @@ enum
 	RC_CTR_CACHE_BLOCKS, RC_CTR_CACHE_TEXELS, RC_CTR_OVERFLOW_EDGES, RC_CTR_OVERFLOW_EVENTS,
 	RC_CTR_OVERFLOW_STACK, RC_CTR_OVERFLOW_CANDS, RC_CTR_SERIAL_LINES, RC_CTR_SORTED_LINES, RC_CTR_UNSTAGED_BANDS,
 	RC_CTR_MAX_CANDS /* most faces one view listed */, RC_CTR_MAX_EDGES /* most edges one view emitted */, RC_CTR_MAX_BAND_EVENTS /* most event slots one band wanted */,
-	RC_CTR_OVERFLOW_CACHE /* (face, mip) blocks k_cache_build could not build */, RC_CTR_TRIS, RC_CTR_TRI_PIXELS, RC_CTR_WIDE_LINES /* scanlines k_lines_wide took */, RC_CTR_OVERFLOW_FIX, RC_CTR_FIXED_FACES, RC_CTR_COUNT = 64 /* 16.. = debug-build phase clocks */
+	RC_CTR_OVERFLOW_CACHE /* (face, mip) blocks k_cache_build could not build */, RC_CTR_TRIS, RC_CTR_TRI_PIXELS, RC_CTR_WIDE_LINES /* scanlines k_lines_wide took */, RC_CTR_OVERFLOW_FIX, RC_CTR_FIXED_FACES,
+	RC_CTR_TRI_WRITTEN /* pixels k_tri_resolve shaded (the key path's visible fragments) */, RC_CTR_BIG_TRIS /* triangles k_tris_fast_big took */, RC_CTR_COUNT = 64 /* 16.. = debug-build phase clocks */
 };
 
 #ifdef __cplusplus

@@ -11,6 +11,8 @@ import ctypes as C
 import functools
 import importlib
 
+import math
+
 import numpy as np
 
 from .hostlib import Host, REF_CUDA_PATH, REF_SOFT_PATH, RF_DRAW_WORLD, calc_fov_y
@@ -36,7 +38,7 @@ assert C.sizeof(RefViewpass) == 56
 
 CTR_NAMES = ["views", "pixels", "cands", "surfs", "edges", "spans", "cache_blocks", "cache_texels",
              "overflow_edges", "overflow_events", "overflow_stack", "overflow_cands", "serial_lines", "sorted_lines", "unstaged_bands",
-             "max_cands", "max_edges", "max_band_events", "overflow_cache", "tris", "tri_pixels", "wide_lines", "overflow_fix", "fixed_faces"]
+             "max_cands", "max_edges", "max_band_events", "overflow_cache", "tris", "tri_pixels", "wide_lines", "overflow_fix", "fixed_faces", "tri_written", "big_tris"]
 
 
 @functools.lru_cache(maxsize=8)
@@ -219,11 +221,11 @@ class Renderer:
             raise RuntimeError("RefCuda_RenderViews failed")
 
     def bench_resident(self, iters, rebuild_cache=False, flush_l2=False, overlap=False, serial_cache=False):
-        """CUDA-event ms per iteration of the last batch re-run with inputs resident in HBM: (total, [5 stages: vis_walk,
-        faces_edges, surface_cache, spans, draw]).  overlap=True: the slicing RefCuda_RenderViews uses for host outputs (4 view
+        """CUDA-event ms per iteration of the last batch re-run with inputs resident in HBM: (total, [6 stages: vis_walk,
+        faces_edges, surface_cache, spans, draw, entities]).  overlap=True: the slicing RefCuda_RenderViews uses for host outputs (4 view
         slices on 2 streams): total only, the stage list is zeros."""
         tot = C.c_float()
-        st = (C.c_float * 5)()
+        st = (C.c_float * 6)()
         if self._bench(iters, (1 if rebuild_cache else 0) | (2 if flush_l2 else 0) | (4 if overlap else 0) | (8 if serial_cache else 0), C.byref(tot), st) != 0:
             raise RuntimeError("RefCuda_BenchResident failed")
         return tot.value, list(st)
@@ -254,6 +256,52 @@ class Renderer:
 
     def device_name(self) -> str:
         return self._devname().decode()
+
+
+def add_studio_models(r, cams, count=64, nbones=32, ahead=72.0, drop=56.0, mdl=None, animtime=0.5):
+    """BASELINE config C4's entities: `count` instances of the synthetic skinned model (tools/mdlgen.py: `nbones`
+    bones, ~1500 vertices, two meshes) standing `ahead` units in front of the first `count` cameras, each at its own
+    yaw and animation phase.  The same call on a ref_cuda and a ref_soft Renderer gives both the same scene."""
+    from .tools import mdlgen
+    if mdl is None:
+        mdl = mdlgen.generate(nbones=nbones)
+    mi = r.load_studio("models/synth.mdl", mdl)
+    cams = np.asarray(cams, dtype=np.float32).reshape(-1, 6)
+    for k in range(count):
+        c = cams[k % len(cams)]
+        yaw = math.radians(float(c[4]))
+        org = (c[0] + ahead * math.cos(yaw), c[1] + ahead * math.sin(yaw), c[2] - drop)
+        r.add_entity(mi, org, angles=(0.0, 37.0 * k, 0.0), frame=(k * 3) % 30, framerate=1.0, animtime=animtime + 0.01 * (k % 16))
+    return mi
+
+
+def sprite_image(seed, w=64, h=64):
+    """a synthetic RGBA sprite frame: a soft disc with noise, transparent outside"""
+    rng = np.random.default_rng(seed)
+    y, x = np.mgrid[0:h, 0:w]
+    d = np.hypot(x - w / 2, y - h / 2) / (w / 2)
+    img = np.zeros((h, w, 4), np.uint8)
+    img[..., 0] = np.clip(255 * (1 - d) + rng.integers(0, 40, (h, w)), 0, 255)
+    img[..., 1] = np.clip(200 * (1 - d * d), 0, 255)
+    img[..., 2] = rng.integers(0, 255, (h, w))
+    img[..., 3] = np.where(d < 0.9, 255, 0)
+    return img
+
+
+def add_sprites(r, cams, count=32, ahead=96.0):
+    """BASELINE config C5's sprites: `count` translucent sprites (additive, alpha-tested texture and colour-blended, all
+    parallel-oriented) `ahead` units in front of the first `count` cameras; sorted per view by the renderer."""
+    TF_HAS_ALPHA = 1 << 20
+    mods = [r.create_sprite("spr_c5_add", sprite_image(11), sprtype=2, texformat=1),
+            r.create_sprite("spr_c5_alpha", sprite_image(12), sprtype=2, texformat=3, texflags=TF_HAS_ALPHA),
+            r.create_sprite("spr_c5_blend", sprite_image(13, 32, 48), sprtype=2, texformat=0)]
+    cams = np.asarray(cams, dtype=np.float32).reshape(-1, 6)
+    for k in range(count):
+        c = cams[k % len(cams)]
+        yaw = math.radians(float(c[4]))
+        org = (c[0] + ahead * math.cos(yaw), c[1] + ahead * math.sin(yaw), c[2] - 8.0 + 4.0 * (k % 5))
+        r.add_entity(mods[k % 3], org, rendermode=[5, 4, 2][k % 3], renderamt=[255, 255, 160][k % 3],
+                     rendercolor=[(255, 200, 120), (255, 255, 255), (90, 200, 255)][k % 3], scale=[1.0, 0.75, 1.5][k % 3])
 
 
 def compare_frames(a_col, a_z, b_col, b_z):
