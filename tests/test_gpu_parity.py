@@ -516,3 +516,56 @@ def test_models_and_sprites_together_match_oracle(pkg, scene):
     cc, cz = cu.render_views(m.cameras[:32])
     rc, rz = so.render_views(m.cameras[:32])
     assert np.array_equal(cc, rc) and np.array_equal(cz, rz), ((cc == rc).mean(), (cz == rz).mean())
+
+
+def test_light_gamma_change_between_batches(pkg, scene):
+    """V_CheckGamma rebuilds the engine's tables in place and calls R_GammaChanged( false ): ref_soft reads the live
+    table (r_local.h:518), the plugin's device copy must follow and every cache block is relit."""
+    m = scene.make_map("tiny", ncameras=16)  # its styled lights go through the table
+    cu = scene.Renderer(pkg.REF_CUDA_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    a0, _ = cu.render_views(m.cameras[:8])
+    r0, _ = so.render_views(m.cameras[:8])
+    assert np.array_equal(a0, r0)
+    for r in (cu, so):
+        r.gamma_changed(gamma=2.2, brightness=0.0, texgamma=2.0, lightgamma=1.8)
+    a1, az1 = cu.render_views(m.cameras[:8])
+    r1, rz1 = so.render_views(m.cameras[:8])
+    assert not np.array_equal(r1, r0), "the oracle did not relight"
+    assert np.array_equal(a1, r1) and np.array_equal(az1, rz1)
+
+
+def test_hud_pass_matches_oracle(pkg, scene):
+    """R_DrawStretchPic (opaque, alpha-channel, tinted, additive, clipped at every screen border) and
+    FillRGBA after the view, through the stock R_BeginFrame .. R_EndFrame loop: the software surfaces are identical."""
+    TF_HAS_ALPHA = 1 << 20
+    m = scene.make_map("small", ncameras=16)
+    rs = []
+    for path in (pkg.REF_CUDA_PATH, pkg.REF_SOFT_PATH):
+        r = scene.Renderer(path, 320, 240, m)
+        opaque = r.load_pic("hud/opaque", scene.sprite_image(5, 48, 40)[..., :4] | np.array([0, 0, 0, 255], np.uint8))
+        alpha = r.load_pic("hud/alpha", scene.sprite_image(6, 64, 64), TF_HAS_ALPHA)
+        hud = [
+            [0, 0, 255, 255, 255, 255, 10, 10, 48, 40, 0, 0, 1, 1, opaque],          # kRenderNormal, 1:1
+            [0, 0, 255, 255, 255, 255, 100, 20, 96, 60, 0.25, 0.25, 0.75, 1, opaque],  # stretched sub-rectangle
+            [0, 4, 255, 160, 60, 255, 200, 100, 64, 64, 0, 0, 1, 1, alpha],           # kRenderTransAlpha, tinted, alpha plane
+            [0, 5, 255, 255, 255, 200, 40, 120, 80, 80, 0, 0, 1, 1, alpha],           # kRenderTransAdd
+            [0, 2, 255, 255, 255, 128, 150, 150, 64, 32, 0, 0, 1, 1, opaque],          # kRenderTransTexture at half alpha
+            [0, 0, 255, 255, 255, 255, -20, 60, 64, 64, 0, 0, 1, 1, alpha],           # clipped left
+            [0, 0, 255, 255, 255, 255, 290, -16, 64, 64, 0, 0, 1, 1, alpha],          # clipped right and top
+            [0, 0, 255, 255, 255, 255, 130, 210, 64, 64, 0, 0, 1, 1, opaque],          # clipped bottom
+            [1, 2, 255, 0, 0, 128, 0, 200, 320, 40, 0, 0, 0, 0, 0],                   # FillRGBA blended
+            [1, 5, 0, 90, 255, 255, 250, 0, 100, 100, 0, 0, 0, 0, 0],                 # FillRGBA additive, clipped
+            [1, 0, 20, 200, 20, 255, -5, -5, 30, 30, 0, 0, 0, 0, 0],                  # FillRGBA opaque, clipped
+        ]
+        rs.append((r, hud))
+    (cu, hud_c), (so, hud_s) = rs
+    bare = so.frame_views(m.cameras[:3])
+    a = cu.frame_views_hud(m.cameras[:3], hud_c)
+    b = so.frame_views_hud(m.cameras[:3], hud_s)
+    assert (b != bare).mean() > 0.15, "the oracle drew no HUD"
+    assert np.array_equal(a, b), (a == b).mean()
+    # VID_ScreenShot of that last frame: the image handed to the engine's writer
+    sa, sb = cu.screenshot(), so.screenshot()
+    assert sa.shape == sb.shape and np.array_equal(sa, sb)
+    assert len(np.unique(sb)) > 64

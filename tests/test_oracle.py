@@ -131,3 +131,18 @@ def test_scalar_studio_path_matches_oracle(pkg, scene, fastkeys, monkeypatch):
     assert (rc != bare).mean() > 0.03, "the oracle drew no models"
     assert np.array_equal(a, rc) and np.array_equal(az, rz)
     assert emu.counters()["tris"] > 1000
+
+
+def test_light_gamma_change_reaches_the_stage_functions(pkg, scene):
+    """same as the GPU test of the name, through the CPU debug harness: the host side resends the 2 KB table"""
+    m = scene.make_map("tiny", ncameras=16)
+    emu = scene.Renderer(EMU_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    r0, _ = so.render_views(m.cameras[:4])
+    emu.render_views(m.cameras[:4])
+    for r in (emu, so):
+        r.gamma_changed(gamma=2.2, brightness=0.0, texgamma=2.0, lightgamma=1.8)
+    a1, az1 = emu.render_views(m.cameras[:4])
+    r1, rz1 = so.render_views(m.cameras[:4])
+    assert not np.array_equal(r1, r0)
+    assert np.array_equal(a1, r1) and np.array_equal(az1, rz1)

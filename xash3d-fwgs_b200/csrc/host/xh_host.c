@@ -310,6 +310,48 @@ static intptr_t (*const xh_stubs[XH_NSTUBS])( void ) = {
 static mspriteframe_t *xh_R_GetSpriteFrame( const model_t *pModel, int frame, float yaw );
 static void *xh_R_StudioGetAnim( studiohdr_t *hdr, model_t *mod, mstudioseqdesc_t *pseqdesc );
 
+/* screenshots: FS_SaveImage keeps the image the renderer hands over (VID_ScreenShot, ref/soft/r_glblit.c:748) */
+static struct { rgbdata_t *pic; byte *data; int width, height, type; size_t size; } xh_shot;
+static qboolean xh_FS_SaveImage( const char *filename, rgbdata_t *pix )
+{
+	(void)filename;
+	free( xh_shot.data );
+	xh_shot.pic = pix; xh_shot.width = pix->width; xh_shot.height = pix->height; xh_shot.type = pix->type; xh_shot.size = pix->size;
+	xh_shot.data = malloc( pix->size );
+	memcpy( xh_shot.data, pix->buffer, pix->size );
+	return true;
+}
+static void xh_FS_FreeImage_any( rgbdata_t *pic )
+{
+	if( pic && pic == xh_shot.pic ) /* allocated by the renderer from a memory pool, not by the harness's loader */
+	{
+		xh_Mem_Free( pic->buffer, __FILE__, __LINE__ ); xh_Mem_Free( pic, __FILE__, __LINE__ );
+		xh_shot.pic = NULL;
+		return;
+	}
+	xh_FS_FreeImage( pic );
+}
+static const bpc_desc_t *xh_Image_GetPFDesc( int idx )
+{
+	static bpc_desc_t d;
+	d.format = idx; d.bpp = ( idx == PF_RGB_24 || idx == PF_BGR_24 ) ? 3 : ( idx == PF_INDEXED_24 || idx == PF_INDEXED_32 ) ? 1 : 4;
+	return &d;
+}
+static void xh_AllowDirectPaths( qboolean enable ) { (void)enable; }
+static fs_api_t xh_fsapi;
+
+/* VID_ScreenShot of the last frame; the image FS_SaveImage received -> out (BGRA), returns its byte size or < 0 */
+int xh_screenshot( int shot_type, void *out, size_t cap, int *width, int *height )
+{
+	if( !xh.ref.VID_ScreenShot( "shot.bmp", shot_type ) || !xh_shot.data )
+		return -1;
+	if( width ) *width = xh_shot.width;
+	if( height ) *height = xh_shot.height;
+	if( xh_shot.size > cap ) return -2;
+	memcpy( out, xh_shot.data, xh_shot.size );
+	return (int)xh_shot.size;
+}
+
 static void xh_fill_engfuncs( ref_api_t *e )
 {
 	/* every slot is a pointer: point all of them at numbered traps first */
@@ -373,7 +415,9 @@ static void xh_fill_engfuncs( ref_api_t *e )
 	e->Image_Process = xh_Image_Process;
 	e->FS_LoadImage = xh_FS_LoadImage;
 	e->FS_CopyImage = xh_FS_CopyImage;
-	e->FS_FreeImage = xh_FS_FreeImage;
+	e->FS_FreeImage = xh_FS_FreeImage_any;
+	e->FS_SaveImage = xh_FS_SaveImage;
+	e->Image_GetPFDesc = xh_Image_GetPFDesc;
 	e->Image_SetMDLPointer = xh_Image_SetMDLPointer;
 	e->EV_GetPhysent = xh_EV_GetPhysent;
 	e->SetLocalLightLevel = xh_SetLocalLightLevel;
@@ -391,7 +435,8 @@ static void xh_fill_engfuncs( ref_api_t *e )
 	e->pfnDrawNormalTriangles = xh_void;
 	e->pfnDrawTransparentTriangles = xh_void;
 	e->drawFuncs = &xh.drawfuncs; /* non-NULL struct of NULL hooks (cl_render.c) */
-	e->fsapi = NULL;
+	xh_fsapi.AllowDirectPaths = xh_AllowDirectPaths;
+	e->fsapi = &xh_fsapi;
 }
 
 /* ------------------------------------------------------------------ */
@@ -534,6 +579,14 @@ uint64_t xh_callback_count( void ) { return xh.callbacks; }
 /* ------------------------------------------------------------------ */
 /* time / light styles                                                   */
 
+/* V_CheckGamma (engine/client/gamma.c:117-141): new tables, then the renderer is told */
+void xh_gamma_changed( float gamma, float brightness, float texgamma, float lightgamma )
+{
+	xh_build_gamma( gamma, brightness, texgamma, lightgamma );
+	if( xh.ref.R_GammaChanged )
+		xh.ref.R_GammaChanged( false );
+}
+
 void xh_set_time( double time, double oldtime )
 {
 	xh.cl.time = time; xh.cl.oldtime = oldtime;
@@ -585,6 +638,46 @@ int xh_frame_views( const float *cams, int n, float fov_x, float fov_y, int x, i
 		const float *c = cams + 6 * i;
 		xh.ref.R_BeginFrame( false );
 		xh_render_view( c, c + 3, fov_x, fov_y, x, y, w, h, flags );
+		xh.ref.R_EndFrame();
+		if( !xh.swbuffer )
+			return -1;
+		size_t bytes = (size_t)xh.sw_w * xh.sw_h * xh.sw_bpp;
+		memcpy((char *)display_out + bytes * i, xh.swbuffer, bytes );
+	}
+	return 0;
+}
+
+/* a HUD picture: an RGBA image handed to the renderer (the engine's pfnSPR_Load / Draw_* paths end in GL_LoadTexture*) */
+int xh_load_pic( const char *name, int w, int h, const void *rgba, int texflags )
+{
+	return xh.ref.GL_CreateTexture( name, w, h, rgba, texflags );
+}
+
+/* one frame as the engine drives it, with a HUD pass: R_BeginFrame, R_Set2DMode( false ) + the view (V_RenderView),
+ * R_Set2DMode( true ) + the 2-D draws (V_PostRender / SCR_UpdateScreen), R_EndFrame.
+ * hud: nhud x 15 floats {kind 0 pic / 1 fill, rendermode, r, g, b, a, x, y, w, h, s1, t1, s2, t2, texnum} */
+int xh_frame_views_hud( const float *cams, int n, float fov_x, float fov_y, int x, int y, int w, int h, int flags,
+	const float *hud, int nhud, void *display_out )
+{
+	for( int i = 0; i < n; i++ )
+	{
+		const float *c = cams + 6 * i;
+		xh.ref.R_BeginFrame( false );
+		xh.ref.R_Set2DMode( false );
+		xh_render_view( c, c + 3, fov_x, fov_y, x, y, w, h, flags );
+		xh.ref.R_Set2DMode( true );
+		for( int k = 0; k < nhud; k++ )
+		{
+			const float *q = hud + 15 * k;
+			if( (int)q[0] == 1 )
+				xh.ref.FillRGBA( (int)q[1], q[6], q[7], q[8], q[9], (byte)q[2], (byte)q[3], (byte)q[4], (byte)q[5] );
+			else
+			{
+				xh.ref.GL_SetRenderMode( (int)q[1] );
+				xh.ref.Color4ub( (byte)q[2], (byte)q[3], (byte)q[4], (byte)q[5] );
+				xh.ref.R_DrawStretchPic( q[6], q[7], q[8], q[9], q[10], q[11], q[12], q[13], (int)q[14] );
+			}
+		}
 		xh.ref.R_EndFrame();
 		if( !xh.swbuffer )
 			return -1;

@@ -73,6 +73,11 @@ XH_EXPORT int xh_point_in_leaf( const float *p, int *contents, int *cluster );
 XH_EXPORT int xh_surface_info( int surf, int *out, int n ); /* flags,extents,lightextents,styles,texnum,... */
 XH_EXPORT const void *xh_gamma_table( int which, int *count ); /* 0 tex(u8) 1 light 2 linear 3 screen (u16) */
 XH_EXPORT void xh_build_gamma( float gamma, float brightness, float texgamma, float lightgamma );
+XH_EXPORT int xh_load_pic( const char *name, int w, int h, const void *rgba, int texflags );
+XH_EXPORT int xh_frame_views_hud( const float *cams, int n, float fov_x, float fov_y, int x, int y, int w, int h, int flags,
+	const float *hud, int nhud, void *display_out );
+XH_EXPORT int xh_screenshot( int shot_type, void *out, size_t cap, int *width, int *height );
+XH_EXPORT void xh_gamma_changed( float gamma, float brightness, float texgamma, float lightgamma );
 XH_EXPORT uint64_t xh_callback_count( void );            /* engine callbacks hit since init (debug) */
 XH_EXPORT const char *xh_last_error( void );
 /* oracle-only probe: CACHESPOT(surf)[mip] of ref_soft -> surface cache block (r_local.h:781-793,968) */

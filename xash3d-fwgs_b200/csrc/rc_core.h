@@ -1026,7 +1026,9 @@ typedef struct
 
 RC_HD int32_t rc_span_kind( const rc_surf_t *sf )
 {
-	if( sf->flags & RC_SURF_DRAWSKY ) return RC_KIND_SKY;
+	/* a solid face without a cache block (lightmap sample size other than 16: R_NewMap reports them) is filled flat
+	 * like a hole in the map - the cache arena is never indexed with its "no block" offset */
+	if(( sf->flags & RC_SURF_DRAWSKY ) || sf->cache_ofs < 0 ) return RC_KIND_SKY;
 	if( sf->flags & RC_SURF_DRAWTURB ) return RC_KIND_TURB;
 	return RC_KIND_SOLID;
 }

@@ -614,6 +614,7 @@ struct Dev
 	int nfast_items = 0, fast_tris = 0;  /* leading opaque run */
 	unsigned long long *d_trikeys = nullptr; size_t cap_trikeys = 0;
 	int32_t *d_biglist = nullptr; size_t cap_big = 0;
+	rc_cmd2d_t *d_cmds2d = nullptr;
 	int32_t *d_item_order = nullptr; rc_poly_t *d_polys = nullptr;
 	size_t cap_item_order = 0, cap_polys = 0;
 
@@ -1037,7 +1038,7 @@ void rc_dev_shutdown( void )
 	cudaDeviceSynchronize();
 	free_batch();
 	/* everything rc_dev_init / the uploads created, so that R_Shutdown + R_Init (vid_restart) starts clean */
-	void **ptrs[] = { (void **)&D.d_trikeys, (void **)&D.d_biglist, (void **)&D.d_sstatic, (void **)&D.d_parts, (void **)&D.d_bones, (void **)&D.d_blight, (void **)&D.d_mvpos, (void **)&D.d_mlight, (void **)&D.d_item_order, (void **)&D.d_polys, (void **)&D.d_alphamap, (void **)&D.d_addmap, (void **)&D.d_modmap, (void **)&D.d_items, (void **)&D.d_corners, (void **)&D.d_sortents, (void **)&D.d_display, (void **)&D.d_screenmap, (void **)&D.d_dlights, (void **)&D.d_dlightbits,
+	void **ptrs[] = { (void **)&D.d_cmds2d, (void **)&D.d_trikeys, (void **)&D.d_biglist, (void **)&D.d_sstatic, (void **)&D.d_parts, (void **)&D.d_bones, (void **)&D.d_blight, (void **)&D.d_mvpos, (void **)&D.d_mlight, (void **)&D.d_item_order, (void **)&D.d_polys, (void **)&D.d_alphamap, (void **)&D.d_addmap, (void **)&D.d_modmap, (void **)&D.d_items, (void **)&D.d_corners, (void **)&D.d_sortents, (void **)&D.d_display, (void **)&D.d_screenmap, (void **)&D.d_dlights, (void **)&D.d_dlightbits,
 		(void **)&D.d_colormap, (void **)&D.d_lightgamma, (void **)&D.d_sintable, (void **)&D.d_textures, (void **)&D.d_texels,
 		(void **)&D.d_styles, (void **)&D.d_keys, (void **)&D.d_need, (void **)&D.d_list, (void **)&D.d_nlist,
 		(void **)&D.d_counters, &D.d_flush };
@@ -1204,6 +1205,25 @@ int rc_dev_set_items( const rc_item_t *items, int nitems, const rc_corner_t *cor
 	for( int i = 0; i < nitems && items[i].drawer == RC_DRAW_FILL && items[i].sortent < 0; i++ ) { D.nfast_items++; D.fast_tris += items[i].count; }
 	if( D.fast_tris < 64 ) D.nfast_items = D.fast_tris = 0;
 	D.h2d_bytes += sizeof( rc_item_t ) * (size_t)nitems + sizeof( rc_corner_t ) * (size_t)ncorners + sizeof( rc_sortent_t ) * (size_t)nsortents;
+	return 0;
+}
+
+int rc_dev_draw2d( const rc_cmd2d_t *cmds, int n, int view )
+{
+	if( !D.have_batch || view < 0 || view >= D.w.nviews ) { snprintf( D.err, sizeof( D.err ), "rc_dev_draw2d: no such frame" ); return -1; }
+	if( n <= 0 ) return 0;
+	if( upload( &D.d_cmds2d, cmds, (size_t)n ) != 0 ) return -1;
+	const rc_work_t ws = make_slice( 0, 0, D.w.nviews );
+	for( int i = 0; i < n; i++ )
+	{
+		const int px = cmds[i].w * cmds[i].height;
+		if( px <= 0 ) continue;
+		int blocks = ( px + 255 ) / 256;
+		if( blocks > D.num_sms * 8 ) blocks = D.num_sms * 8;
+		k_2d<<<blocks, 256, 0, D.stream>>>( D.sc, ws, D.d_cmds2d, i, view ); D.launches++;
+	}
+	KCHECK( "k_2d", D.stream );
+	CK( cudaStreamSynchronize( D.stream ));
 	return 0;
 }
 

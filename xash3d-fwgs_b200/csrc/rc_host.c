@@ -84,6 +84,7 @@ static struct
 	uint16_t     colormap[32 * 8192];
 	int32_t      sintable[1280];
 	const uint16_t *lightgamma; /* engine table */
+	uint16_t lightgamma_sent[1024]; /* what the device has */
 
 	int          lightstylevalue[MAX_LIGHTSTYLES];
 
@@ -96,6 +97,8 @@ static struct
 	/* view queue between R_BeginFrame and R_EndFrame */
 	rc_view_t   *views;
 	int          nviews, maxviews;
+	int          screen_view, screen_valid; /* the frame of the last batch R_EndFrame showed (VID_ScreenShot) */
+	rc_cmd2d_t  *cmds2d; int ncmds2d, maxcmds2d; /* the frame's HUD pass (R_DrawStretchPic / FillRGBA), applied in R_EndFrame */
 
 	void        *swbuffer_info_valid;
 	int          had_dlights;
@@ -603,6 +606,7 @@ static void R_NewMap( void )
 	rc.surf_texnum = rc_malloc( sizeof( int32_t ) * Q_max( 1, w->numsurfaces ));
 	rc_surface_t *surfs = rc_malloc( sizeof( rc_surface_t ) * Q_max( 1, w->numsurfaces ));
 	size_t cache_texels = 0;
+	int unsupported = 0;
 	for( int i = 0; i < w->numsurfaces; i++ )
 	{
 		const msurface_t *s = &w->surfaces[i];
@@ -636,6 +640,8 @@ static void R_NewMap( void )
 		}
 		/* every (face,mip) block gets a fixed home in the cache arena: 180 GB of HBM removes the need for the
 		 * reference's ring allocator and its evictions (D_SCAlloc, ref/soft/r_surf.c:833) */
+		if( !FBitSet( s->flags, SURF_DRAWSKY | SURF_DRAWTURB ) && d->sample_size != 16 )
+			unsupported++;
 		for( int m = 0; m < 4; m++ )
 		{
 			d->cache_ofs[m] = -1;
@@ -648,6 +654,9 @@ static void R_NewMap( void )
 		}
 	}
 	sc.lightdata_len = (int)lightlen;
+	if( unsupported )
+		gEngfuncs.Con_Printf( S_WARN "ref_cuda: %d faces use a lightmap sample size other than 16 (R_DrawSurfaceBlock8_Generic, ref/soft/r_surf.c:345): "
+			"not built yet, they are filled flat\n", unsupported );
 
 	sc.planes = planes; sc.nodes = nodes; sc.leafs = leafs; sc.surfaces = surfs; sc.marksurfaces = marks;
 	sc.surfedges = w->surfedges; sc.edges = edges; sc.verts = (const float *)w->vertexes;
@@ -1062,6 +1071,12 @@ static void rc_tri_color4f( float rr, float gg, float bb, float aa )
 	}
 	unsigned short r = rr * 31, g = gg * 63, b = bb * 31;
 	rc.tri.color = rc_encode565( Q_min( r, 31 ), Q_min( g, 63 ), Q_min( b, 31 ));
+}
+
+/* _TriColor4ub (ref/soft/r_triapi.c:143) */
+static void rc_tri_color4ub( unsigned char r, unsigned char g, unsigned char b, unsigned char a )
+{
+	rc_tri_color4f( r * ( 1.0f / 255.0f ), g * ( 1.0f / 255.0f ), b * ( 1.0f / 255.0f ), a * ( 1.0f / 255.0f ));
 }
 
 static void TriColor4ub( unsigned char r, unsigned char g, unsigned char b, unsigned char a )
@@ -1886,10 +1901,35 @@ static void rc_add_studio( cl_entity_t *e )
 	}
 }
 
+/* LightToTexGamma (ref/soft/r_local.h:518-523) reads the engine's live table, or nothing in linear gamma space */
+static void rc_resolve_lightgamma( void )
+{
+	static uint16_t identity[1024];
+	rc.lightgamma = (const uint16_t *)gEngfuncs.EngineGetParm( PARM_GET_LIGHTGAMMATABLE_PTR, 0 );
+	if( !rc.lightgamma || FBitSet( gp_host->features, ENGINE_LINEAR_GAMMA_SPACE ))
+	{
+		for( int i = 0; i < 1024; i++ ) identity[i] = i;
+		rc.lightgamma = identity;
+	}
+}
+
+/* the device keeps a copy of the 2 KB table: V_CheckGamma rebuilds the engine's in place (gamma.c:135-139) and
+ * host.features can change when a game loads - resend it when either happened, and relight every cache block */
+static void rc_sync_lightgamma( void )
+{
+	rc_resolve_lightgamma();
+	if( !memcmp( rc.lightgamma_sent, rc.lightgamma, sizeof( rc.lightgamma_sent )))
+		return;
+	memcpy( rc.lightgamma_sent, rc.lightgamma, sizeof( rc.lightgamma_sent ));
+	RC_CHECK_DEV( rc_dev_upload_luts( rc.colormap, rc.lightgamma, rc.sintable ));
+	RC_CHECK_DEV( rc_dev_flush_cache());
+}
+
 static void rc_prepare_batch( void )
 {
 	if( !rc.scene_valid )
 		gEngfuncs.Host_Error( "ref_cuda: render without a world (R_NewMap not called)\n" );
+	rc_sync_lightgamma();
 	rc_sync_textures();
 	rc_resolve_texnums( false );
 	RC_CHECK_DEV( rc_dev_set_lightstyles( rc.lightstylevalue ));
@@ -1908,7 +1948,9 @@ static void rc_queue_view( const ref_viewpass_t *rvp )
 	rc_setup_view( rvp, &rc.views[rc.nviews++] );
 }
 
-static void R_BeginFrame( qboolean clearScene ) { (void)clearScene; rc.nviews = 0; }
+static void R_Set2DMode( qboolean enable );
+static void rc_flush_2d( int view );
+static void R_BeginFrame( qboolean clearScene ) { (void)clearScene; rc.nviews = 0; rc.ncmds2d = 0; R_Set2DMode( true ); }
 
 /* GL_RenderFrame slot == R_RenderFrame (ref/soft/r_main.c:1141): here the view is only recorded */
 static void R_RenderFrame( const ref_viewpass_t *rvp )
@@ -1999,9 +2041,11 @@ static void R_EndFrame( void )
 		rc_prepare_batch();
 		/* the frames stay in HBM; the display conversion reads them there */
 		RC_CHECK_DEV( rc_dev_render( rc.views, rc.nviews, w, h, 0, NULL, NULL ));
+		rc_flush_2d( rc.nviews - 1 ); /* the passes share the screen in the reference: the HUD lands on the last one */
 		rc_blit_screen();
+		rc.screen_view = rc.nviews - 1; rc.screen_valid = 1;
 	}
-	rc.nviews = 0;
+	rc.nviews = 0; rc.ncmds2d = 0;
 }
 
 /* ---- batch extension (include/ref_cuda.h) ---- */
@@ -2075,13 +2119,8 @@ static qboolean R_Init( void )
 		return false;
 	}
 
-	rc.lightgamma = (const uint16_t *)gEngfuncs.EngineGetParm( PARM_GET_LIGHTGAMMATABLE_PTR, 0 );
-	static uint16_t identity[1024];
-	if( !rc.lightgamma || FBitSet( gp_host->features, ENGINE_LINEAR_GAMMA_SPACE ))
-	{
-		for( int i = 0; i < 1024; i++ ) identity[i] = i; /* LightToTexGamma is the identity then (r_local.h:518) */
-		rc.lightgamma = identity;
-	}
+	rc_resolve_lightgamma();
+	memcpy( rc.lightgamma_sent, rc.lightgamma, sizeof( rc.lightgamma_sent ));
 
 	rc_build_colormap();
 	for( int i = 0; i < 1280; i++ ) /* R_InitTurb, ref/soft/r_main.c:1312: AMP + sin( i * 3.14159 * 2 / CYCLE ) * AMP */
@@ -2144,7 +2183,7 @@ static qboolean R_SetDisplayTransform( ref_screen_rotation_t rotate, int x, int 
 static void GL_SetupAttributes( int safegl ) { (void)safegl; }
 static void GL_InitExtensions( void ) {}
 static void GL_ClearExtensions( void ) {}
-static void R_GammaChanged( qboolean do_reset_gamma ) { if( !do_reset_gamma ) rc_dev_flush_cache(); }
+static void R_GammaChanged( qboolean do_reset_gamma ) { if( !do_reset_gamma && rc.initialized ) { rc_sync_lightgamma(); rc_dev_flush_cache(); } }
 static void R_PushScene( void ) {}
 static void R_PopScene( void ) {}
 static void GL_BackendStartFrame( void ) {}
@@ -2155,13 +2194,163 @@ static void R_ShowTextures( void ) {}
 static const byte *R_GetTextureOriginalBuffer( unsigned int idx ) { (void)idx; return NULL; }
 static void GL_ProcessTexture( int texnum, float gamma, int topColor, int bottomColor ) { (void)texnum; (void)gamma; (void)topColor; (void)bottomColor; }
 static void R_SetupSky( int *skyboxTextures ) { (void)skyboxTextures; }
-static void R_Set2DMode( qboolean enable ) { (void)enable; }
-static void R_DrawStretchPic( float x, float y, float w, float h, float s1, float t1, float s2, float t2, int texnum )
-{ (void)x; (void)y; (void)w; (void)h; (void)s1; (void)t1; (void)s2; (void)t2; (void)texnum; }
-static void FillRGBA( int rendermode, float x, float y, float w, float h, byte r, byte g, byte b, byte a )
-{ (void)rendermode; (void)x; (void)y; (void)w; (void)h; (void)r; (void)g; (void)b; (void)a; }
+/* R_Set2DMode (ref/soft/r_draw.c:228) */
+static void R_Set2DMode( qboolean enable )
+{
+	rc.tri.color = 0xFFFF; /* COLOR_WHITE */
+	rc.tri.is2d = enable;
+	rc.tri.alpha = 7;
+}
+
+static rc_cmd2d_t *rc_cmd2d_new( void )
+{
+	if( rc.ncmds2d == rc.maxcmds2d )
+	{
+		int n = rc.maxcmds2d ? rc.maxcmds2d * 2 : 64;
+		rc.cmds2d = gEngfuncs._Mem_Realloc( rc.pool, rc.cmds2d, sizeof( rc_cmd2d_t ) * n, true, __FILE__, __LINE__ );
+		rc.maxcmds2d = n;
+	}
+	rc_cmd2d_t *c = &rc.cmds2d[rc.ncmds2d++];
+	memset( c, 0, sizeof( *c ));
+	c->color = rc.tri.color; c->alpha = rc.tri.alpha; c->rendermode = rc.tri.rendermode;
+	return c;
+}
+
+/* R_DrawStretchPic + the clipping half of R_DrawStretchPicImplementation (ref/soft/r_draw.c:38-85,145): the HUD pass is
+ * recorded and applied to the frame on the device once the views are drawn (R_EndFrame), in call order */
+static void R_DrawStretchPic( float fx, float fy, float fw, float fh, float fs1, float ft1, float fs2, float ft2, int texnum )
+{
+	if( texnum < 0 || texnum >= RC_MAX_TEXTURES ) texnum = 0;
+	const rc_image_t *pic = &rc.images[texnum];
+	if( fs2 > 1.0f || ft2 > 1.0f || fs1 < 0.0f || ft1 < 0.0f || fw < 1.0f || fh < 1.0f )
+		return;
+	int x = fx, y = fy, w = fw, h = fh;
+	int s1 = pic->width * fs1, t1 = pic->height * ft1, s2 = pic->width * fs2, t2 = pic->height * ft2;
+	const int vw = gpGlobals->width, vh = gpGlobals->height;
+	if( x < 0 ) { s1 += ( -x ) * ( s2 - s1 ) / w; x = 0; }
+	if( x + w > vw ) { s2 -= ( x + w - vw ) * ( s2 - s1 ) / w; w = vw - x; }
+	if( y + h > vh ) { t2 -= ( y + h - vh ) * ( t2 - t1 ) / h; h = vh - y; }
+	if( !pic->pixels[0] || s1 >= s2 || t1 >= t2 )
+		return;
+	unsigned int height = h;
+	int skip = 0;
+	if( y < -h )
+		return;
+	if( y < 0 ) { skip = -y; height += y; y = 0; }
+	if( w <= 0 || h <= 0 || (int)height <= 0 )
+		return; /* the reference's loops do not run */
+	rc_cmd2d_t *c = rc_cmd2d_new();
+	c->kind = RC_2D_PIC; c->x = x; c->y = y; c->w = w; c->h = h; c->s1 = s1; c->t1 = t1; c->s2 = s2; c->t2 = t2;
+	c->skip = skip; c->height = (int)height;
+	c->tex_ofs = texnum; /* resolved to an arena offset when the pass is sent */
+	c->texwidth = pic->width; c->transparent = pic->alpha_pixels != NULL;
+}
+
+/* CL_FillRGBA + Draw_Fill (ref/soft/r_context.c:44, r_draw.c:159) */
+static void FillRGBA( int rendermode, float fx, float fy, float fw, float fh, byte r, byte g, byte b, byte a )
+{
+	rc.tri.rendermode = rendermode;
+	rc_tri_color4f( r * ( 1.0f / 255.0f ), g * ( 1.0f / 255.0f ), b * ( 1.0f / 255.0f ), a * ( 1.0f / 255.0f ));
+	int x = fx, y = fy, w = fw, h = fh;
+	const int vw = gpGlobals->width, vh = gpGlobals->height;
+	if( x < 0 ) x = 0;
+	if( x + w > vw ) w = vw - x;
+	if( w <= 0 ) return;
+	if( y + h > vh ) h = vh - y;
+	if( h <= 0 ) return;
+	unsigned int height = h;
+	if( y < 0 )
+	{
+		if( h <= -y ) return;
+		height += y; y = 0;
+	}
+	rc_cmd2d_t *c = rc_cmd2d_new();
+	c->kind = RC_2D_FILL; c->x = x; c->y = y; c->w = w; c->h = h; c->height = (int)height; c->tex_ofs = -1;
+}
+
+/* the recorded HUD pass onto frame `view` of the batch in HBM */
+static void rc_flush_2d( int view )
+{
+	int n = 0;
+	for( int i = 0; i < rc.ncmds2d; i++ )
+	{
+		rc_cmd2d_t c = rc.cmds2d[i];
+		if( c.kind == RC_2D_PIC )
+		{
+			const rc_texture_t *t = rc_texture_entry( c.tex_ofs );
+			if( !t ) continue;
+			c.tex_ofs = c.transparent ? t->alpha_ofs : t->ofs[0];
+			if( c.tex_ofs < 0 ) continue;
+		}
+		rc.cmds2d[n++] = c;
+	}
+	if( n ) RC_CHECK_DEV( rc_dev_draw2d( rc.cmds2d, n, view ));
+	rc.ncmds2d = 0;
+}
+
 static int WorldToScreen( const vec3_t world, vec3_t screen ) { (void)world; VectorClear( screen ); return 1; }
-static qboolean VID_ScreenShot( const char *filename, int shot_type ) { (void)filename; (void)shot_type; return false; }
+/* VID_ScreenShot (ref/soft/r_glblit.c:748): the frame last shown, in display colours, bottom row first, as PF_BGRA_32
+ * through the engine's image writer.  The frame is still in HBM: k_blit converts it once more, into the shot. */
+static qboolean VID_ScreenShot( const char *filename, int shot_type )
+{
+	const int vw = gpGlobals->width, vh = gpGlobals->height;
+	if( !rc.screen_valid )
+		return false;
+	uint flags = IMAGE_FLIP_Y;
+	int width = 0, height = 0;
+	rgbdata_t *r_shot = gEngfuncs._Mem_Alloc( rc.pool, sizeof( rgbdata_t ), true, __FILE__, __LINE__ );
+	r_shot->width = ( vw + 3 ) & ~3;
+	r_shot->height = ( vh + 3 ) & ~3;
+	r_shot->flags = IMAGE_HAS_COLOR;
+	r_shot->type = PF_BGRA_32;
+	r_shot->size = r_shot->width * r_shot->height * gEngfuncs.Image_GetPFDesc( r_shot->type )->bpp;
+	r_shot->palette = NULL;
+	r_shot->buffer = gEngfuncs._Mem_Alloc( rc.pool, r_shot->size, false, __FILE__, __LINE__ );
+
+	byte *disp = rc_malloc((size_t)vw * vh * rc.sw_bpp );
+	RC_CHECK_DEV( rc_set_display_format( rc.sw_bpp, rc.sw_r, rc.sw_g, rc.sw_b ));
+	RC_CHECK_DEV( rc_dev_blit( rc.screen_view, 1, disp, vw, NULL ));
+	uint32_t *pbuf = (uint32_t *)r_shot->buffer;
+	for( int v = 0; v < vh; v++ )
+	{
+		const size_t start = (size_t)vw * ( vh - v - 1 ), dstart = (size_t)rc.sw_stride * v;
+		for( int u = 0; u < vw; u++ )
+		{
+			uint32_t s32;
+			if( rc.sw_bpp == 2 )
+			{
+				const uint color = ((const uint16_t *)disp )[start + u];
+				const uint c0 = (((( color >> 11 ) & 0x1F ) * 527 ) + 23 ) >> 6, c1 = (((( color >> 5 ) & 0x3F ) * 259 ) + 33 ) >> 6, c2 = ((( color & 0x1F ) * 527 ) + 23 ) >> 6;
+				s32 = ( c0 & 0xFF ) << 16 | ( c1 & 0xFF ) << 8 | ( c2 & 0xFF );
+			}
+			else
+				s32 = ((const uint32_t *)disp )[start + u];
+			pbuf[dstart + u] = s32 | 0xFF000000u;
+		}
+	}
+	rc_free( disp );
+
+	switch( shot_type )
+	{
+	case VID_SCREENSHOT: break;
+	case VID_SNAPSHOT: gEngfuncs.fsapi->AllowDirectPaths( true ); break;
+	case VID_LEVELSHOT:
+	case VID_MINISHOT:
+		flags |= IMAGE_RESAMPLE;
+		height = shot_type == VID_MINISHOT ? 200 : 480;
+		width = Q_rint( height * ((double)r_shot->width / r_shot->height ));
+		break;
+	case VID_MAPSHOT:
+		flags |= IMAGE_RESAMPLE | IMAGE_QUANTIZE;
+		height = 768; width = 1024;
+		break;
+	}
+	gEngfuncs.Image_Process( &r_shot, width, height, flags, 0.0f );
+	qboolean result = gEngfuncs.FS_SaveImage( filename, r_shot );
+	gEngfuncs.fsapi->AllowDirectPaths( false );
+	gEngfuncs.FS_FreeImage( r_shot );
+	return result;
+}
 static qboolean VID_CubemapShot( const char *base, uint size, const float *vieworg, qboolean skyshot ) { (void)base; (void)size; (void)vieworg; (void)skyshot; return false; }
 static colorVec R_LightPoint( const float *p ) { colorVec c = { 255, 255, 255, 255 }; (void)p; return c; }
 static void R_DecalShoot( int textureIndex, int entityIndex, int modelIndex, vec3_t pos, int flags, float scale )
@@ -2286,7 +2475,7 @@ static const ref_interface_t gReffuncs =
 	.GL_UpdateTexture = GL_UpdateTexture, .GL_Bind = GL_Bind,
 	.GL_RenderFrame = R_RenderFrame, .GL_OrthoBounds = GL_OrthoBounds, .R_SpeedsMessage = R_SpeedsMessage,
 	.Mod_GetCurrentVis = Mod_GetCurrentVis, .R_NewMap = R_NewMap, .R_ClearScene = R_ClearScene,
-	.TriRenderMode = TriRenderMode, .Begin = TriBegin, .End = TriEnd, .Color4f = TriColor4f, .Color4ub = TriColor4ub,
+	.TriRenderMode = TriRenderMode, .Begin = TriBegin, .End = TriEnd, .Color4f = rc_tri_color4f, .Color4ub = rc_tri_color4ub, /* _TriColor4f / _TriColor4ub (r_context.c:523) */
 	.Vertex3fv = TriVertex3fv, .Vertex3f = TriVertex3f, .CullFace = TriCullFace,
 	.R_FillRenderAPI = R_FillRenderAPI, .R_FillTriAPI = R_FillTriAPI, .VGUI_SetupDrawing = VGUI_SetupDrawing,
 };

@@ -420,4 +420,19 @@ __global__ void __launch_bounds__( 128 ) k_tri_resolve( rc_scene_t sc, rc_work_t
 	if(( threadIdx.x & 31 ) == 0 && nw ) atomicAdd( &w.counters[RC_CTR_TRI_WRITTEN], (unsigned long long)nw );
 }
 
+/* ---------------------------------------------------------------------------------------------- */
+/* the HUD pass: one launch per command (they overlap and their order is the result), thread per destination pixel */
+__global__ void __launch_bounds__( 256 ) k_2d( rc_scene_t sc, rc_work_t w, const rc_cmd2d_t *cmds, int which, int view )
+{
+	const rc_cmd2d_t c = cmds[which];
+	const rc_blendluts_t L = { sc.colormap, w.alphamap, w.addmap, w.modmap };
+	const int32_t n = c.height * c.w;
+	uint16_t *frame = w.color + (size_t)view * w.width * w.height;
+	for( int32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x )
+	{
+		const int32_t v = i / c.w, u = i - v * c.w;
+		rc_2d_pixel( &L, &c, sc.texels, v, (uint32_t)u, frame + (size_t)( c.y + v ) * w.width + c.x + u );
+	}
+}
+
 #endif /* RC_K_TRIS_CUH */

@@ -225,6 +225,20 @@ typedef struct
 	int32_t pad[1];
 } rc_sortent_t; /* 32 B */
 
+/* a 2-D draw of the frame's HUD pass (R_DrawStretchPic / Draw_Fill, ref/soft/r_draw.c:38,159), clipped on the host */
+enum { RC_2D_PIC = 0, RC_2D_FILL = 1 };
+typedef struct
+{
+	int32_t kind;             /* RC_2D_* */
+	int32_t x, y, w, h;       /* destination after clipping (h: the unclipped height the row step divides by) */
+	int32_t s1, t1, s2, t2;   /* source rectangle in texels */
+	int32_t skip, height;     /* rows cut off above the screen, rows drawn */
+	int32_t tex_ofs, texwidth;/* pixels[0] or alpha_pixels in the texel arena */
+	int32_t transparent;      /* source carries 3 alpha bits on top (alpha_pixels) */
+	int32_t color, alpha, rendermode; /* vid.color, vid.alpha, vid.rendermode when the call was made */
+	int32_t pad;
+} rc_cmd2d_t; /* 72 B */
+
 /* a face the BSP walk decided to draw, in front-to-back order (R_RecursiveWorldNode -> R_RenderFace) */
 typedef struct
 {

@@ -500,6 +500,44 @@ RC_HD void rc_tri_shade( const rc_blendluts_t *L, int drawer, uint32_t color, ui
 }
 
 /* ------------------------------------------------------------------------------------------ */
+/* the HUD pass: one destination pixel of R_DrawStretchPicImplementation / Draw_Fill (ref/soft/r_draw.c:88-135,192-210) */
+RC_HD void rc_2d_pixel( const rc_blendluts_t *L, const rc_cmd2d_t *c, const uint16_t *texels, int32_t v, uint32_t u, uint16_t *dest )
+{
+	uint32_t src;
+	int32_t alpha = c->alpha;
+	if( c->kind == RC_2D_PIC )
+	{
+		const uint32_t sv = (uint32_t)(( c->skip + v ) * ( c->t2 - c->t1 ) / c->h + c->t1 );
+		const uint32_t fstep = (uint32_t)((( c->s2 - c->s1 ) << 16 ) / c->w );
+		const uint32_t f = u * fstep; /* f += fstep, u times */
+		src = texels[(size_t)c->tex_ofs + (size_t)sv * (uint32_t)c->texwidth + (uint32_t)c->s1 + ( f >> 16 )];
+		if( c->transparent )
+		{
+			alpha &= (int32_t)( src >> 13 );
+			src = ( src << 3 ) & 0xFFFFu;
+		}
+		if( alpha == 0 )
+			return;
+		if( (uint32_t)c->color != 0xFFFFu )
+			src = rc_blend_color( L, src, (uint32_t)c->color );
+	}
+	else
+	{
+		src = (uint32_t)c->color;
+		if( alpha == 0 )
+			return;
+	}
+	if( c->rendermode == 5 ) /* kRenderTransAdd */
+		*dest = (uint16_t)rc_blend_add( L, src, *dest );
+	else if( c->kind == RC_2D_PIC && c->rendermode == 0x1000 ) /* kRenderScreenFadeModulate */
+		*dest = (uint16_t)rc_blend_color( L, *dest, (uint32_t)c->color );
+	else if( alpha < 7 )
+		*dest = (uint16_t)rc_blend_alpha( L, (uint32_t)alpha, src, *dest );
+	else
+		*dest = (uint16_t)src;
+}
+
+/* ------------------------------------------------------------------------------------------ */
 /* studio models: R_StudioDrawPoints' per-vertex and per-normal work (ref/soft/r_studio.c:1802-1895)  */
 
 /* Matrix3x4_VectorTransform (public/xash3d_mathlib.h:255): a studio vertex through its bone */

@@ -79,6 +79,12 @@ class Renderer:
     def set_time(self, t):
         self.host.set_time(t)
 
+    def gamma_changed(self, gamma=2.5, brightness=0.0, texgamma=2.0, lightgamma=2.5):
+        """the engine's V_CheckGamma: the four gamma tables rebuilt in place, then R_GammaChanged( false )"""
+        L = self.host.lib
+        L.xh_gamma_changed.argtypes = [C.c_float] * 4
+        L.xh_gamma_changed(gamma, brightness, texgamma, lightgamma)
+
     def set_lightstyle(self, i, pattern, time=0.0):
         self.host.set_lightstyle(i, pattern, time)
 
@@ -207,6 +213,42 @@ class Renderer:
                             RF_DRAW_WORLD, disp.ctypes.data) != 0:
             raise RuntimeError("xh_frame_views failed")
         return disp
+
+    def load_pic(self, name, rgba, texflags=0):
+        """an RGBA image (h, w, 4 uint8) as a renderer texture (HUD pictures) -> texture number"""
+        rgba = np.ascontiguousarray(rgba, dtype=np.uint8)
+        L = self.host.lib
+        L.xh_load_pic.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        t = L.xh_load_pic(name.encode(), rgba.shape[1], rgba.shape[0], rgba.ctypes.data, texflags)
+        if t <= 0:
+            raise RuntimeError("xh_load_pic failed")
+        return t
+
+    def frame_views_hud(self, cams, hud, fov_x=90.0):
+        """frame_views with a HUD pass after every view.  hud: rows of {kind 0 pic / 1 fill, rendermode, r, g, b, a, x, y, w, h,
+        s1, t1, s2, t2, texnum}: GL_SetRenderMode + Color4ub + R_DrawStretchPic, or FillRGBA."""
+        cams = np.ascontiguousarray(np.asarray(cams, dtype=np.float32).reshape(-1, 6))
+        hud = np.ascontiguousarray(np.asarray(hud, dtype=np.float32).reshape(-1, 15))
+        n = len(cams)
+        disp = np.empty((n, self.height, self.width), np.uint16 if self.host.sw_format[0] == 2 else np.uint32)
+        L = self.host.lib
+        L.xh_frame_views_hud.argtypes = [C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                         C.c_void_p, C.c_int, C.c_void_p]
+        if L.xh_frame_views_hud(cams.ctypes.data, n, fov_x, calc_fov_y(fov_x, self.width, self.height), 0, 0, self.width, self.height,
+                                RF_DRAW_WORLD, hud.ctypes.data, len(hud), disp.ctypes.data) != 0:
+            raise RuntimeError("xh_frame_views_hud failed")
+        return disp
+
+    def screenshot(self, shot_type=0):
+        """VID_ScreenShot of the frame last shown by R_EndFrame -> the BGRA image FS_SaveImage received, array[h, w] uint32"""
+        L = self.host.lib
+        L.xh_screenshot.argtypes = [C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
+        buf = np.empty(((self.height + 3) & ~3) * ((self.width + 3) & ~3), np.uint32)
+        w, h = C.c_int(), C.c_int()
+        n = L.xh_screenshot(shot_type, buf.ctypes.data, buf.nbytes, C.byref(w), C.byref(h))
+        if n < 0:
+            raise RuntimeError(f"xh_screenshot failed ({n})")
+        return buf[: w.value * h.value].reshape(h.value, w.value)
 
     def render_resident(self, cams, fov_x=90.0, clear=True):
         """Render with the results left in HBM (no device->host copy)."""
