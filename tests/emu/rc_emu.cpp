@@ -477,7 +477,7 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 							if( kind == RC_KIND_SKY ) color[p] = (uint16_t)c.base;
 							else
 							{
-								int32_t ti = rc_pixel_texel( &c, i, turb );
+								int32_t ti = ( kind == RC_KIND_SOLID && vw->texfilt ) ? rc_pixel_texel_filt( &c, i, n, sp.u, y ) : rc_pixel_texel( &c, i, turb );
 								color[p] = kind == RC_KIND_TURB ? E.texels[ti] : E.cache[ti];
 							}
 						}

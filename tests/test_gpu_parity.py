@@ -299,12 +299,13 @@ def test_c5_4096_views_with_water_match_oracle(pkg, scene):
         assert np.array_equal(a[lo : lo + 512], rc) and np.array_equal(az[lo : lo + 512], rz), lo
 
 
-@pytest.mark.parametrize("case", ["fov60", "fov110", "roll", "mipcap2", "mipscale05", "novis", "fullbright", "in_solid"])
+@pytest.mark.parametrize("case", ["fov60", "fov110", "roll", "mipcap2", "mipscale05", "novis", "fullbright", "in_solid", "texfilt"])
 def test_view_and_cvar_variants_match_oracle(pkg, scene, case):
     """Inputs the C2 camera list never has: other fields of view, camera roll, sw_mipcap / sw_mipscale, r_novis,
-    r_fullbright, an eye inside solid."""
+    r_fullbright, an eye inside solid, sw_texfilt (D_DrawSpans16's dithered texel fetch)."""
     m = scene.make_map("small", ncameras=32)
-    cv = {"mipcap2": {"sw_mipcap": 2}, "mipscale05": {"sw_mipscale": 0.5}, "novis": {"r_novis": 1}, "fullbright": {"r_fullbright": 1}}.get(case, {})
+    cv = {"mipcap2": {"sw_mipcap": 2}, "mipscale05": {"sw_mipscale": 0.5}, "novis": {"r_novis": 1}, "fullbright": {"r_fullbright": 1},
+          "texfilt": {"sw_texfilt": 1}}.get(case, {})
     cu = scene.Renderer(pkg.REF_CUDA_PATH, 320, 240, m, cvars=cv)
     so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m, cvars=cv)
     cams = np.array(m.cameras[:16], dtype=np.float32)

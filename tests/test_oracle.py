@@ -146,3 +146,16 @@ def test_light_gamma_change_reaches_the_stage_functions(pkg, scene):
     r1, rz1 = so.render_views(m.cameras[:4])
     assert not np.array_equal(r1, r0)
     assert np.array_equal(a1, r1) and np.array_equal(az1, rz1)
+
+
+def test_texture_dither_matches_oracle_on_cpu(pkg, scene):
+    """sw_texfilt 1: rc_texfilt_index (the 2x2 dither kernel of D_DrawSpans16, r_scan.c:503-672) through the CPU harness"""
+    m = scene.make_map("tiny", ncameras=16)
+    emu = scene.Renderer(EMU_PATH, 320, 240, m, cvars={"sw_texfilt": 1})
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m, cvars={"sw_texfilt": 1})
+    plain = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    a, az = emu.render_views(m.cameras[:4])
+    rc, rz = so.render_views(m.cameras[:4])
+    p, _ = plain.render_views(m.cameras[:4])
+    assert not np.array_equal(p, rc), "sw_texfilt had no effect on the oracle"
+    assert np.array_equal(a, rc) and np.array_equal(az, rz)

@@ -1164,6 +1164,29 @@ RC_HD int32_t rc_pixel_texel( const rc_chunk_t *c, int32_t i, const int32_t *tur
 	return c->base + ( s >> 16 ) + ( t >> 16 ) * c->width;
 }
 
+/* sw_texfilt 1 (D_DrawSpans16's second drawing loop, r_scan.c:652-672): the texel coordinates of a solid pixel are
+ * nudged by a 2x2 ordered-dither kernel before they are truncated.  X = ( pspan->u + spancount ) & 1 with spancount the
+ * pixels left in the 8-pixel chunk, pspan->u the SPAN's first column (same parity as the chunk's); Y = pspan->v & 1. */
+RC_HD int32_t rc_texfilt_index( int32_t s, int32_t t, int32_t width, int32_t X, int32_t Y )
+{
+	/* kernel[X][Y][0 / 1] = { { {16384, 0}, {49152, 32768} }, { {32768, 49152}, {0, 16384} } } */
+	const int32_t q = ( X << 1 ) | Y;
+	const int32_t ks = q == 0 ? 16384 : q == 1 ? 49152 : q == 2 ? 32768 : 0;
+	const int32_t kt = q == 0 ? 0 : q == 1 ? 32768 : q == 2 ? 49152 : 16384;
+	int32_t is = (int32_t)((uint32_t)s + (uint32_t)ks ) >> 16, it = (int32_t)((uint32_t)t + (uint32_t)kt ) >> 16;
+	is = is ? is - 1 : is;
+	it = it ? it - 1 : it;
+	return is + it * width;
+}
+
+/* pixel i of an n-pixel chunk of a solid span that starts at column u_span of scanline v */
+RC_HD int32_t rc_pixel_texel_filt( const rc_chunk_t *c, int32_t i, int32_t n, int32_t u_span, int32_t v )
+{
+	int32_t s = (int32_t)((uint32_t)c->s + (uint32_t)i * (uint32_t)c->sstep );
+	int32_t t = (int32_t)((uint32_t)c->t + (uint32_t)i * (uint32_t)c->tstep );
+	return c->base + rc_texfilt_index( s, t, c->width, ( u_span + ( n - i )) & 1, v & 1 );
+}
+
 RC_HD int16_t rc_pixel_z( const rc_chunk_t *c, int32_t i )
 {
 	return (int16_t)((int32_t)((uint32_t)c->izi + (uint32_t)i * (uint32_t)c->izistep ) >> 16 );

@@ -90,9 +90,12 @@ struct rc_work_t
 	const uint16_t *alphamap; const uint8_t *addmap, *modmap;
 	int32_t    nfast_items, fast_tris;  /* the leading run of opaque items: k_tris_fast instead of k_tris_ordered */
 	unsigned long long *trikeys;        /* [nviews][height][width] z << 32 | triangle number */
+	int32_t   *pairs, *pair_count;      /* k_item_cull: the (view << 16 | item) pairs of the opaque run that survive the cull */
 	int32_t   *big_list, *big_count; int32_t big_cap; /* triangles k_tris_fast hands to k_tris_fast_big: {view, key number} */
 	/* studio models (k_studio_points) */
 	const uint8_t *sstatic; const rc_spart_t *parts; const float *bones, *blight; float *mvpos; int32_t *mlight;
+	int32_t   *partbox;                 /* [nparts][6] bounding box of the part's transformed vertices as ordered int keys */
+	uint8_t   *itemvis;                 /* [nviews][nitems] k_item_cull: 0 = no triangle of the item can be drawn in the view */
 };
 
 #define SP_LINES 32 /* scanlines per band (rc_k_spans.cuh): k_faces bins edges by band */
@@ -615,6 +618,8 @@ struct Dev
 	unsigned long long *d_trikeys = nullptr; size_t cap_trikeys = 0;
 	int32_t *d_biglist = nullptr; size_t cap_big = 0;
 	rc_cmd2d_t *d_cmds2d = nullptr;
+	int32_t *d_pairs = nullptr; size_t cap_pairs = 0; int fast_maxcount = 0;
+	int32_t *d_partbox = nullptr; size_t cap_partbox = 0; uint8_t *d_itemvis = nullptr; size_t cap_itemvis = 0;
 	int32_t *d_item_order = nullptr; rc_poly_t *d_polys = nullptr;
 	size_t cap_item_order = 0, cap_polys = 0;
 
@@ -816,7 +821,7 @@ rc_work_t make_slice( int k, int v0, int v1 )
 	ws.candof += (size_t)v0 * ( sc.numsurfaces + 2 );
 	ws.facerecs += (size_t)v0 * ws.max_cands;
 	ws.facewrote += (size_t)v0 * ws.max_cands;
-	ws.fix_list += (size_t)3 * ws.fix_cap * k; ws.fix_count = D.d_nlist + 8 * k + 7;
+	ws.fix_list += (size_t)3 * ws.fix_cap * k; ws.fix_count = D.d_nlist + 16 * k + 7;
 	ws.edges += (size_t)v0 * ws.max_edges;
 	ws.ncands += v0; ws.nedges += v0;
 	ws.bandnloc += (size_t)v0 * ws.nbands;
@@ -828,7 +833,7 @@ rc_work_t make_slice( int k, int v0, int v1 )
 	ws.cache_need = D.d_need + (size_t)k * ( nslots / 32 + 2 );
 	ws.cache_keys = D.d_keys;
 	ws.cache_list = D.d_list + (size_t)k * nslots;
-	ws.cache_nlist = D.d_nlist + 8 * k; ws.cache_cursor = ws.cache_nlist + 1; ws.line_cursor = ws.cache_nlist + 2; ws.heavy_count = ws.cache_nlist + 5; ws.wide_count = ws.cache_nlist + 6;
+	ws.cache_nlist = D.d_nlist + 16 * k; ws.cache_cursor = ws.cache_nlist + 1; ws.line_cursor = ws.cache_nlist + 2; ws.heavy_count = ws.cache_nlist + 5; ws.wide_count = ws.cache_nlist + 6;
 	ws.heavy_list += (size_t)v0 * ws.height;
 	ws.wide_list += (size_t)v0 * ws.height;
 	ws.styles = D.d_styles; ws.counters = D.d_counters;
@@ -840,7 +845,9 @@ rc_work_t make_slice( int k, int v0, int v1 )
 	ws.nfast_items = D.nfast_items; ws.fast_tris = D.fast_tris;
 	ws.trikeys = D.d_trikeys ? D.d_trikeys + (size_t)v0 * ws.width * ws.height : nullptr;
 	ws.big_cap = (int32_t)( D.cap_big / RC_MAX_SLICES ); ws.big_list = D.d_biglist ? D.d_biglist + (size_t)2 * ws.big_cap * k : nullptr;
-	ws.big_count = D.d_nlist + 8 * k + 3; /* line_cursor[1] is free again once k_lines is done */
+	ws.big_count = D.d_nlist + 16 * k + 8; ws.pair_count = D.d_nlist + 16 * k + 9;
+	ws.pairs = D.d_pairs ? D.d_pairs + (size_t)v0 * ( D.nfast_items > 0 ? D.nfast_items : 1 ) : nullptr;
+	ws.partbox = D.d_partbox; ws.itemvis = D.d_itemvis ? D.d_itemvis + (size_t)v0 * D.nitems : nullptr;
 	ws.sstatic = D.d_sstatic; ws.parts = D.d_parts; ws.bones = D.d_bones; ws.blight = D.d_blight; ws.mvpos = D.d_mvpos; ws.mlight = D.d_mlight;
 	return ws;
 }
@@ -852,6 +859,7 @@ int launch_studio_points( cudaStream_t st )
 		return 0;
 	const rc_work_t ws = make_slice( 0, 0, D.w.nviews );
 	const int np = D.totalverts + D.totalnorms;
+	k_partbox_init<<<( D.nparts * 6 + 255 ) / 256, 256, 0, st>>>( ws, D.nparts ); D.launches++;
 	k_studio_points<<<( np + 255 ) / 256, 256, 0, st>>>( D.sc, ws, D.nparts, D.totalverts, D.totalnorms ); D.launches++;
 	KCHECK( "k_studio_points", st );
 	D.studio_dirty = false;
@@ -863,7 +871,7 @@ int launch_slice( const rc_work_t &ws, int k, cudaStream_t st, cudaEvent_t *evs,
 {
 	const rc_scene_t &sc = D.sc;
 	CK( cudaMemsetAsync( ws.cache_need, 0, sizeof( uint32_t ) * (( sc.numsurfaces * 4 + 31 ) / 32 + 1 ), st ));
-	CK( cudaMemsetAsync( ws.cache_nlist, 0, sizeof( int32_t ) * 8, st ));
+	CK( cudaMemsetAsync( ws.cache_nlist, 0, sizeof( int32_t ) * 16, st ));
 	if( evs ) CK( cudaEventRecord( evs[0], st ));
 	k_viswalk<VW_NTHREADS><<<ws.nviews < D.vw_grid ? ws.nviews : D.vw_grid, VW_NTHREADS, (size_t)ws.vis_smem, st>>>( sc, ws );
 	D.launches++;
@@ -917,11 +925,12 @@ int launch_slice( const rc_work_t &ws, int k, cudaStream_t st, cudaEvent_t *evs,
 		{
 			/* entities: after the world's spans are in the frame (R_DrawEntitiesOnList follows R_EdgeDrawing, r_main.c:1090) */
 			if( launch_studio_points( st ) != 0 ) return -1;
+			k_item_cull<<<( ws.nviews * D.nitems + 127 ) / 128, 128, 0, st>>>( ws ); D.launches++;
 			if( D.fast_tris )
 			{
-				CK( cudaMemsetAsync( ws.big_count, 0, sizeof( int32_t ), st ));
 				k_tri_keys_init<<<D.num_sms * 8, 256, 0, st>>>( ws ); D.launches++;
-				dim3 gf(( D.fast_tris + 127 ) / 128, ws.nviews );
+				/* x = slot in the pair list (the live ones first; the rest of the upper bound exits at once), y = 128 triangles */
+				dim3 gf( ws.nviews * D.nfast_items, ( D.fast_maxcount + 127 ) / 128 );
 				k_tris_fast<<<gf, 128, 0, st>>>( ws ); D.launches++;
 				KCHECK( "k_tris_fast", st );
 				k_tris_fast_big<<<D.num_sms * 8, 128, 0, st>>>( ws ); D.launches++;
@@ -1027,7 +1036,7 @@ int rc_dev_init( int device )
 	if( upload( &D.d_styles, D.h_styles, 256 ) != 0 ) return -1;
 	if( dalloc( &D.d_counters, RC_CTR_COUNT ) != 0 ) return -1;
 	CK( cudaMemset( D.d_counters, 0, sizeof( unsigned long long ) * RC_CTR_COUNT ));
-	if( dalloc( &D.d_nlist, 8 * RC_MAX_SLICES ) != 0 ) return -1;
+	if( dalloc( &D.d_nlist, 16 * RC_MAX_SLICES ) != 0 ) return -1;
 	D.ready = true;
 	return 0;
 }
@@ -1038,7 +1047,7 @@ void rc_dev_shutdown( void )
 	cudaDeviceSynchronize();
 	free_batch();
 	/* everything rc_dev_init / the uploads created, so that R_Shutdown + R_Init (vid_restart) starts clean */
-	void **ptrs[] = { (void **)&D.d_cmds2d, (void **)&D.d_trikeys, (void **)&D.d_biglist, (void **)&D.d_sstatic, (void **)&D.d_parts, (void **)&D.d_bones, (void **)&D.d_blight, (void **)&D.d_mvpos, (void **)&D.d_mlight, (void **)&D.d_item_order, (void **)&D.d_polys, (void **)&D.d_alphamap, (void **)&D.d_addmap, (void **)&D.d_modmap, (void **)&D.d_items, (void **)&D.d_corners, (void **)&D.d_sortents, (void **)&D.d_display, (void **)&D.d_screenmap, (void **)&D.d_dlights, (void **)&D.d_dlightbits,
+	void **ptrs[] = { (void **)&D.d_pairs, (void **)&D.d_partbox, (void **)&D.d_itemvis, (void **)&D.d_cmds2d, (void **)&D.d_trikeys, (void **)&D.d_biglist, (void **)&D.d_sstatic, (void **)&D.d_parts, (void **)&D.d_bones, (void **)&D.d_blight, (void **)&D.d_mvpos, (void **)&D.d_mlight, (void **)&D.d_item_order, (void **)&D.d_polys, (void **)&D.d_alphamap, (void **)&D.d_addmap, (void **)&D.d_modmap, (void **)&D.d_items, (void **)&D.d_corners, (void **)&D.d_sortents, (void **)&D.d_display, (void **)&D.d_screenmap, (void **)&D.d_dlights, (void **)&D.d_dlightbits,
 		(void **)&D.d_colormap, (void **)&D.d_lightgamma, (void **)&D.d_sintable, (void **)&D.d_textures, (void **)&D.d_texels,
 		(void **)&D.d_styles, (void **)&D.d_keys, (void **)&D.d_need, (void **)&D.d_list, (void **)&D.d_nlist,
 		(void **)&D.d_counters, &D.d_flush };
@@ -1048,7 +1057,7 @@ void rc_dev_shutdown( void )
 	D.cap_cands = D.cap_edges = D.cap_blk_events = 0; D.caps_dirty = false;
 	D.nitems = D.ncorners = D.nsortents = 0; D.h_items.clear(); D.ntris = 0; D.cap_item_order = D.cap_polys = 0;
 	D.nparts = D.totalverts = D.totalnorms = 0; D.cap_mvpos = D.cap_mlight = 0; D.studio_dirty = false;
-	D.nfast_items = D.fast_tris = 0; D.cap_trikeys = D.cap_big = 0;
+	D.nfast_items = D.fast_tris = 0; D.cap_trikeys = D.cap_big = 0; D.cap_partbox = D.cap_itemvis = D.cap_pairs = 0;
 	D.display_bytes = 0; D.ndlights = 0; D.screen_bpp = 0; D.cache_texels = 0; D.ntextures = 0;
 	D.sc = rc_scene_t{}; D.h_surfaces.clear(); D.h_textures.clear();
 	cudaStream_t *streams[] = { &D.stream, &D.copy };
@@ -1203,7 +1212,9 @@ int rc_dev_set_items( const rc_item_t *items, int nitems, const rc_corner_t *cor
 	/* the leading run of opaque, fixed-order items takes the order-free path when it is worth its key buffer */
 	D.nfast_items = D.fast_tris = 0;
 	for( int i = 0; i < nitems && items[i].drawer == RC_DRAW_FILL && items[i].sortent < 0; i++ ) { D.nfast_items++; D.fast_tris += items[i].count; }
-	if( D.fast_tris < 64 ) D.nfast_items = D.fast_tris = 0;
+	if( D.fast_tris < 64 || D.nfast_items > 65535 ) D.nfast_items = D.fast_tris = 0;
+	D.fast_maxcount = 0;
+	for( int i = 0; i < D.nfast_items; i++ ) if( items[i].count > D.fast_maxcount ) D.fast_maxcount = items[i].count;
 	D.h2d_bytes += sizeof( rc_item_t ) * (size_t)nitems + sizeof( rc_corner_t ) * (size_t)ncorners + sizeof( rc_sortent_t ) * (size_t)nsortents;
 	return 0;
 }
@@ -1247,6 +1258,7 @@ int rc_dev_set_studio( const rc_spart_t *parts, int nparts, const float *bones, 
 	if( (size_t)totalverts * 3 > D.cap_mvpos ) { if( dalloc( &D.d_mvpos, (size_t)totalverts * 3 ) != 0 ) return -1; D.cap_mvpos = (size_t)totalverts * 3; }
 	if( (size_t)totalnorms > D.cap_mlight ) { if( dalloc( &D.d_mlight, (size_t)totalnorms ) != 0 ) return -1; D.cap_mlight = (size_t)totalnorms; }
 	D.h2d_bytes += sizeof( rc_spart_t ) * (size_t)nparts + sizeof( float ) * 15 * (size_t)nbones;
+	if( (size_t)nparts * 6 > D.cap_partbox ) { if( dalloc( &D.d_partbox, (size_t)nparts * 6 + 6 ) != 0 ) return -1; D.cap_partbox = (size_t)nparts * 6; }
 	D.studio_dirty = true;
 	return 0;
 }
@@ -1311,12 +1323,16 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 		if( ensure_batch( nviews, width, height ) != 0 ) return -1;
 		if( D.nitems && D.ntris )
 		{
+			const size_t need_v = (size_t)D.cap_views * D.nitems;
+			if( need_v > D.cap_itemvis ) { if( dalloc( &D.d_itemvis, need_v ) != 0 ) return -1; D.cap_itemvis = need_v; }
 			const size_t need_o = (size_t)D.cap_views * D.nitems, need_p = (size_t)D.cap_views * ( D.ntris - D.fast_tris ) + 1;
 			if( D.fast_tris )
 			{
 				const size_t need_k = (size_t)D.cap_views * width * height, need_b = (size_t)RC_MAX_SLICES * ( (size_t)D.cap_views * 4096 + 65536 );
 				if( need_k > D.cap_trikeys ) { if( dalloc( &D.d_trikeys, need_k ) != 0 ) return -1; D.cap_trikeys = need_k; }
 				if( need_b > D.cap_big ) { if( dalloc( &D.d_biglist, 2 * need_b ) != 0 ) return -1; D.cap_big = need_b; }
+				const size_t need_pr = (size_t)D.cap_views * D.nfast_items;
+				if( need_pr > D.cap_pairs ) { if( dalloc( &D.d_pairs, need_pr ) != 0 ) return -1; D.cap_pairs = need_pr; }
 			}
 			if( need_o > D.cap_item_order ) { if( dalloc( &D.d_item_order, need_o ) != 0 ) return -1; D.cap_item_order = need_o; }
 			if( need_p > D.cap_polys ) { if( dalloc( &D.d_polys, need_p ) != 0 ) return -1; D.cap_polys = need_p; }

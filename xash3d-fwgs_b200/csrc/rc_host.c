@@ -54,6 +54,7 @@ static ref_host_t   *gp_host;
 
 static CVAR_DEFINE_AUTO( sw_clearcolor, "48999", 0, "screen clear color" );
 static CVAR_DEFINE_AUTO( sw_mipcap, "0", FCVAR_GLCONFIG, "" );
+static CVAR_DEFINE_AUTO( sw_texfilt, "0", FCVAR_GLCONFIG, "texture dither" );
 static CVAR_DEFINE_AUTO( sw_mipscale, "1", FCVAR_GLCONFIG, "nothing" );
 static CVAR_DEFINE_AUTO( sw_noalphabrushes, "0", FCVAR_GLCONFIG, "" );
 static CVAR_DEFINE_AUTO( cu_device, "0", FCVAR_GLCONFIG, "CUDA device ordinal used by ref_cuda" );
@@ -640,12 +641,13 @@ static void R_NewMap( void )
 		}
 		/* every (face,mip) block gets a fixed home in the cache arena: 180 GB of HBM removes the need for the
 		 * reference's ring allocator and its evictions (D_SCAlloc, ref/soft/r_surf.c:833) */
-		if( !FBitSet( s->flags, SURF_DRAWSKY | SURF_DRAWTURB ) && d->sample_size != 16 )
+		const qboolean nocache = d->sample_size != 16 || FBitSet( s->flags, SURF_CONVEYOR );
+		if( !FBitSet( s->flags, SURF_DRAWSKY | SURF_DRAWTURB ) && nocache )
 			unsupported++;
 		for( int m = 0; m < 4; m++ )
 		{
 			d->cache_ofs[m] = -1;
-			if( FBitSet( s->flags, SURF_DRAWSKY | SURF_DRAWTURB ) || d->sample_size != 16 )
+			if( FBitSet( s->flags, SURF_DRAWSKY | SURF_DRAWTURB ) || nocache )
 				continue;
 			int cw = info->lightextents[0] >> m, ch = info->lightextents[1] >> m;
 			if( cw <= 0 || ch <= 0 ) continue;
@@ -655,8 +657,8 @@ static void R_NewMap( void )
 	}
 	sc.lightdata_len = (int)lightlen;
 	if( unsupported )
-		gEngfuncs.Con_Printf( S_WARN "ref_cuda: %d faces use a lightmap sample size other than 16 (R_DrawSurfaceBlock8_Generic, ref/soft/r_surf.c:345): "
-			"not built yet, they are filled flat\n", unsupported );
+		gEngfuncs.Con_Printf( S_WARN "ref_cuda: %d faces use a lightmap sample size other than 16 (R_DrawSurfaceBlock8_Generic, ref/soft/r_surf.c:345) or are conveyors "
+			"(r_surf.c:1065): not built yet, they are filled flat\n", unsupported );
 
 	sc.planes = planes; sc.nodes = nodes; sc.leafs = leafs; sc.surfaces = surfs; sc.marksurfaces = marks;
 	sc.surfedges = w->surfedges; sc.edges = edges; sc.verts = (const float *)w->vertexes;
@@ -831,6 +833,7 @@ static void rc_setup_view( const ref_viewpass_t *rvp, rc_view_t *v )
 
 	v->turb_phase = (int)( gp_cl->time * 20 ) & 127; /* SPEED, CYCLE */
 	v->sky_color = (int)sw_clearcolor.value & 0xFFFF;
+	v->texfilt = sw_texfilt.value == 1.0f;
 	v->flags = rvp->flags;
 	v->pvs_radius = r_novis.value ? -1.0f : r_pvs_radius->value;
 }
@@ -1031,7 +1034,7 @@ static rc_item_t *rc_new_item( int kind )
 	rc.items = rc_grow( rc.items, &rc.maxitems, rc.nitems + 1, sizeof( rc_item_t ));
 	rc_item_t *it = &rc.items[rc.nitems++];
 	memset( it, 0, sizeof( *it ));
-	it->kind = kind;
+	it->kind = kind; it->part = -1;
 	it->drawer = rc.tri.drawer; it->tex_ofs = rc.tri.texnum; /* texture NUMBER here; resolved to an arena offset when the batch is sent */
 	it->skinwidth = rc.tri.skinwidth; it->skinheight = rc.tri.skinheight;
 	it->color = rc.tri.color; it->alpha = rc.tri.alpha;
@@ -1897,6 +1900,7 @@ static void rc_add_studio( cl_entity_t *e )
 			it->first = rs.sub[si].mesh_first[j];
 			it->count = rs.sub[si].mesh_ntris[j];
 			it->vert_base = pt->vert_base; it->light_base = pt->light_base;
+			it->part = (int)( pt - rs.parts );
 		}
 	}
 }
@@ -2096,6 +2100,7 @@ static qboolean R_Init( void )
 {
 	gEngfuncs.Cvar_RegisterVariable( &sw_clearcolor );
 	gEngfuncs.Cvar_RegisterVariable( &sw_mipcap );
+	gEngfuncs.Cvar_RegisterVariable( &sw_texfilt );
 	gEngfuncs.Cvar_RegisterVariable( &sw_mipscale );
 	gEngfuncs.Cvar_RegisterVariable( &sw_noalphabrushes );
 	gEngfuncs.Cvar_RegisterVariable( &cu_device );

@@ -149,6 +149,7 @@ __global__ void __launch_bounds__( DR_WARPS * 32, 8 ) k_draw( rc_scene_t sc, rc_
 		const rc_surf_t *vsurfs = w.surfs + (size_t)view * w.max_cands;
 		const rc_view_t *vw = &w.views[view];
 		const int32_t *turb = sc.sintable + vw->turb_phase;
+		const bool texfilt = vw->texfilt != 0;
 		uint16_t *crow = w.color + (size_t)line * w.width;
 		uint16_t *zrow = reinterpret_cast<uint16_t *>( w.zbuf ) + (size_t)line * w.width;
 
@@ -370,7 +371,19 @@ __global__ void __launch_bounds__( DR_WARPS * 32, 8 ) k_draw( rc_scene_t sc, rc_
 						const int32_t nmine = min( 4, npx - i0 ); /* pixels of this lane: 4 almost always */
 						uint16_t *cp = crow + x0 + i0, *zp = zrow + x0 + i0;
 						uint32_t col[4];
-						if( kind2 == RC_KIND_SOLID && nmine == 4 )
+						if( kind2 == RC_KIND_SOLID && texfilt )
+						{
+							/* sw_texfilt 1: dithered texel coordinates (rc_texfilt_index) */
+							const uint16_t *blk = cache + (int32_t)B.z;
+							const int32_t ln2 = x0 / w.width, X0 = ( x0 - ln2 * w.width ) + npx - i0, Y = ( y + ln2 ) & 1;
+#pragma unroll
+							for( int i = 0; i < 4; i++ )
+							{
+								col[i] = i < nmine ? (uint32_t)__ldg( blk + rc_texfilt_index( (int32_t)s, (int32_t)t, pitch, ( X0 - i ) & 1, Y )) : 0u;
+								s += A.z; t += A.w;
+							}
+						}
+						else if( kind2 == RC_KIND_SOLID && nmine == 4 )
 						{
 							/* the common case: a full quad from the surface cache, no predicates */
 							const uint16_t *blk = cache + (int32_t)B.z;

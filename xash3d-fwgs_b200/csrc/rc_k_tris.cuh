@@ -117,6 +117,12 @@ __device__ __forceinline__ const rc_item_t *rc_item_of( const rc_work_t &w, int3
 	return &w.items[lo];
 }
 
+__global__ void k_partbox_init( rc_work_t w, int32_t nparts )
+{
+	const int32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+	if( g < nparts * 6 ) w.partbox[g] = ( g % 6 ) < 3 ? 0x7FFFFFFF : (int32_t)0x80000000;
+}
+
 /* R_StudioDrawPoints' vertex and normal loops (r_studio.c:1846-1895) for every drawn (entity, submodel) of the batch, once
  * per batch (they do not depend on the view): thread per vertex, then thread per normal */
 __global__ void __launch_bounds__( 256 ) k_studio_points( rc_scene_t sc, rc_work_t w, int32_t nparts, int32_t totalverts, int32_t totalnorms )
@@ -143,6 +149,22 @@ __global__ void __launch_bounds__( 256 ) k_studio_points( rc_scene_t sc, rc_work
 		rc_studio_vertex( w.bones + (size_t)( pt.bones + w.sstatic[pt.svertbone + i] ) * 12, sf + pt.sverts + 3 * i, out );
 		float *dst = w.mvpos + (size_t)idx * 3;
 		dst[0] = out[0]; dst[1] = out[1]; dst[2] = out[2];
+		/* the part's bounding box for k_item_cull: order-preserving int keys, one atomic pair per axis (per warp when the
+		 * whole warp works on one part) */
+		const unsigned am = __activemask();
+		const bool uniform = __match_any_sync( am, lo ) == am;
+#pragma unroll
+		for( int a = 0; a < 3; a++ )
+		{
+			const int32_t b = __float_as_int( out[a] ), key = b >= 0 ? b : b ^ 0x7FFFFFFF;
+			int32_t kmin = key, kmax = key;
+			if( uniform ) { kmin = __reduce_min_sync( am, key ); kmax = __reduce_max_sync( am, key ); }
+			if( !uniform || ( threadIdx.x & 31 ) == __ffs( (int)am ) - 1 )
+			{
+				atomicMin( &w.partbox[lo * 6 + a], kmin );
+				atomicMax( &w.partbox[lo * 6 + 3 + a], kmax );
+			}
+		}
 	}
 	else
 	{
@@ -151,6 +173,58 @@ __global__ void __launch_bounds__( 256 ) k_studio_points( rc_scene_t sc, rc_work
 		w.mlight[idx] = rc_studio_light( &pt, w.sstatic[pt.snormflags + k], sf + pt.snorms + 3 * k,
 			w.blight + (size_t)( pt.blightvec + w.sstatic[pt.snormbone + k] ) * 3, sc.lightgamma );
 	}
+}
+
+/*
+ * Per (view, item): can any triangle of the item be drawn?  A triangle is dropped when its three final verts share a
+ * clip flag (R_RenderTriangle's trivial reject, rc_view_triangle); every vertex of a studio part lies in the part's box,
+ * and "z < ALIAS_Z_CLIP_PLANE", "u < vrect.x", ... are half-spaces of view space, so a box whose eight corners lie in
+ * one of them (with a pixel of margin for the truncation of u, v) holds only vertices that carry that flag - also the
+ * ones the clipper would make on its edges.  R_StudioDrawModel's own R_StudioCheckBBox plays this part in the reference.
+ */
+__global__ void __launch_bounds__( 128 ) k_item_cull( rc_work_t w )
+{
+	const int32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+	if( g >= w.nviews * w.nitems )
+		return;
+	const int view = g / w.nitems, idx = g - view * w.nitems;
+	const rc_item_t *it = &w.items[idx];
+	uint8_t vis = 1;
+	if( it->kind == RC_ITEM_MESH && it->part >= 0 )
+	{
+		const rc_view_t *vw = &w.views[view];
+		float bb[6];
+#pragma unroll
+		for( int a = 0; a < 6; a++ )
+		{
+			const int32_t key = w.partbox[it->part * 6 + a];
+			bb[a] = __int_as_float( key >= 0 ? key : key ^ 0x7FFFFFFF );
+		}
+		const float xl = vw->xcenter - (float)vw->vrect[0] + 2.0f, xr = vw->xcenter - (float)( vw->vrect[0] + vw->vrect[2] ) - 2.0f;
+		const float yt = vw->ycenter - (float)vw->vrect[1] + 2.0f, yb = vw->ycenter - (float)( vw->vrect[1] + vw->vrect[3] ) - 2.0f;
+		unsigned all = 0x1Fu;
+#pragma unroll
+		for( int c = 0; c < 8; c++ )
+		{
+			const float p[3] = { bb[( c & 1 ) ? 3 : 0], bb[( c & 2 ) ? 4 : 1], bb[( c & 4 ) ? 5 : 2] };
+			const float x = rc_dot3( p, vw->aliastransform[0] ) + vw->aliastransform[0][3];
+			const float y = rc_dot3( p, vw->aliastransform[1] ) + vw->aliastransform[1][3];
+			const float z = rc_dot3( p, vw->aliastransform[2] ) + vw->aliastransform[2][3];
+			const float az = fabsf( z ) * 1e-4f + 1e-3f; /* slack for the rounding of the three products */
+			unsigned f = 0;
+			if( z < RC_ALIAS_Z_CLIP_PLANE - 0.25f ) f |= 1u;
+			if( x * vw->xscale + xl * z < -az * vw->xscale ) f |= 2u;  /* u < vrect.x for every z > 0 */
+			if( x * vw->xscale + xr * z > az * vw->xscale ) f |= 4u;   /* u > vrect.x + vrect.width */
+			if( y * vw->yscale + yt * z < -az * vw->yscale ) f |= 8u;
+			if( y * vw->yscale + yb * z > az * vw->yscale ) f |= 16u;
+			all &= f;
+		}
+		if( all ) vis = 0;
+	}
+	w.itemvis[g] = vis;
+	/* the opaque run: k_tris_fast is launched over the pairs that are left */
+	if( vis && idx < w.nfast_items && it->tex_ofs >= 0 && it->count > 0 )
+		w.pairs[atomicAdd( w.pair_count, 1 )] = ( view << 16 ) | idx;
 }
 
 __global__ void __launch_bounds__( 128 ) k_tri_polys( rc_work_t w, int32_t ntris )
@@ -166,7 +240,8 @@ __global__ void __launch_bounds__( 128 ) k_tri_polys( rc_work_t w, int32_t ntris
 	rc_corner_t c[3];
 	rc_fv_t poly[8];
 	int k = 0;
-	if( it->tex_ofs >= 0 && g - it->order0 < it->count && rc_item_corners( w, vw, it, g - it->order0, c ))
+	if( it->tex_ofs >= 0 && g - it->order0 < it->count && w.itemvis[(size_t)view * w.nitems + ( it - w.items )]
+		&& rc_item_corners( w, vw, it, g - it->order0, c ))
 		k = rc_view_triangle( vw, &c[0], &c[1], &c[2], poly );
 	out->k = k;
 	for( int i = 0; i < k; i++ )
@@ -297,17 +372,23 @@ __device__ __forceinline__ uint32_t rc_fast_row( const rc_trisetup_t *ts, int32_
 
 __global__ void __launch_bounds__( 128 ) k_tris_fast( rc_work_t w )
 {
-	const int view = blockIdx.y;
-	const int32_t g = blockIdx.x * blockDim.x + threadIdx.x;
-	unsigned long long npix = 0, ntri = 0;
-	if( g < w.fast_tris )
+	if( (int32_t)blockIdx.x >= *w.pair_count )
+		return;
+	const int32_t pair = w.pairs[blockIdx.x];
+	const int view = pair >> 16;
+	const rc_item_t *it = &w.items[pair & 0xFFFF];
+	const int32_t tri = blockIdx.y * blockDim.x + threadIdx.x;
+	if( (int32_t)( blockIdx.y * blockDim.x ) >= it->count )
+		return;
+	unsigned npix = 0, ntri = 0;
+	if( tri < it->count )
 	{
-		const rc_item_t *it = rc_item_of( w, g );
+		const int32_t g = it->order0 + tri;
 		const rc_view_t *vw = &w.views[view];
 		rc_corner_t c[3];
 		rc_fv_t poly[8];
 		int k = 0;
-		if( it->tex_ofs >= 0 && g - it->order0 < it->count && rc_item_corners( w, vw, it, g - it->order0, c ))
+		if( rc_item_corners( w, vw, it, tri, c ))
 			k = rc_view_triangle( vw, &c[0], &c[1], &c[2], poly );
 		unsigned long long *keys = w.trikeys + (size_t)view * w.width * w.height;
 		for( int i = 1; i < k - 1; i++ )
@@ -319,11 +400,9 @@ __global__ void __launch_bounds__( 128 ) k_tris_fast( rc_work_t w )
 			int32_t y0;
 			const int32_t rows = rc_tri_rows( &ts, &y0 );
 			const uint32_t id = (uint32_t)g * 8u + (uint32_t)i + 1u;
-			/* a rough pixel count: rows x the widest of the first, middle and last scanline */
-			rc_trirow_t ra, rb, rm;
-			rc_tri_row( &ts, 0, &ra ); rc_tri_row( &ts, rows - 1, &rb ); rc_tri_row( &ts, rows >> 1, &rm );
-			const int32_t wmax = max( max( ra.count, rb.count ), rm.count );
-			if( (long long)rows * wmax > TF_BIG_PIXELS )
+			/* a rough pixel count: the bounding box of the three corners */
+			const int32_t umin = min( poly[0].u, min( poly[i].u, poly[i + 1].u )), umax = max( poly[0].u, max( poly[i].u, poly[i + 1].u ));
+			if( rows * ( umax - umin + 1 ) > TF_BIG_PIXELS )
 			{
 				const int32_t slot = atomicAdd( w.big_count, 1 );
 				if( slot < w.big_cap )
@@ -337,12 +416,11 @@ __global__ void __launch_bounds__( 128 ) k_tris_fast( rc_work_t w )
 		}
 	}
 	/* counters: one atomic per warp */
-	const unsigned m = __activemask();
-	const unsigned np = __reduce_add_sync( m, (unsigned)npix ), nt = __reduce_add_sync( m, (unsigned)ntri );
-	if(( threadIdx.x & 31 ) == __ffs( (int)m ) - 1 )
+	npix = __reduce_add_sync( 0xFFFFFFFFu, npix ); ntri = __reduce_add_sync( 0xFFFFFFFFu, ntri );
+	if(( threadIdx.x & 31 ) == 0 )
 	{
-		if( np ) atomicAdd( &w.counters[RC_CTR_TRI_PIXELS], (unsigned long long)np );
-		if( nt ) atomicAdd( &w.counters[RC_CTR_TRIS], (unsigned long long)nt );
+		if( npix ) atomicAdd( &w.counters[RC_CTR_TRI_PIXELS], (unsigned long long)npix );
+		if( ntri ) atomicAdd( &w.counters[RC_CTR_TRIS], (unsigned long long)ntri );
 	}
 }
 
@@ -380,12 +458,11 @@ __global__ void __launch_bounds__( 128 ) k_tris_fast_big( rc_work_t w )
 		int32_t y0;
 		const int32_t rows = rc_tri_rows( &ts, &y0 );
 		unsigned long long *keys = w.trikeys + (size_t)view * w.width * w.height;
-		for( int32_t r = 0; r < rows; r++ )
-		{
-			const uint32_t cnt = rc_fast_row( &ts, r, keys + (size_t)( y0 + r ) * w.width, id, lane, 32 );
-			if( lane == 0 ) npix += cnt;
-		}
+		/* lane per scanline: the edge stepping of a row costs more than its pixels */
+		for( int32_t r = lane; r < rows; r += 32 )
+			npix += rc_fast_row( &ts, r, keys + (size_t)( y0 + r ) * w.width, id, 0, 1 );
 	}
+	npix = __reduce_add_sync( 0xFFFFFFFFu, (unsigned)npix );
 	if( lane == 0 && npix ) atomicAdd( &w.counters[RC_CTR_TRI_PIXELS], npix );
 }
 

@@ -149,7 +149,7 @@ typedef struct
 	int32_t sky_color;           /* (int)sw_clearcolor & 0xFFFF */
 	int32_t flags;               /* ref_viewpass_t.flags */
 	float   pvs_radius;
-	int32_t pad[1];
+	int32_t texfilt;             /* sw_texfilt == 1: D_DrawSpans16's texture dither (ref/soft/r_scan.c:503-672) */
 	float   aliastransform[3][4]; /* R_SetUpWorldTransform (ref/soft/r_trialias.c:52): world -> view space for R_SetupFinalVert */
 } rc_view_t;
 
@@ -190,7 +190,8 @@ typedef struct
 	float   sr, cr;               /* SPR_FWD_PARALLEL_ORIENTED: SinCos of the roll */
 	/* RC_ITEM_MESH: the entity's slices of the batch's transformed vertices and per-normal lights */
 	int32_t vert_base, light_base;
-	int32_t pad[2];
+	int32_t part;                 /* RC_ITEM_MESH: index of its (entity, submodel) in the batch's part list; else -1 */
+	int32_t pad[1];
 } rc_item_t; /* 160 B */
 
 /* a studio submodel as the device keeps it (static per model file): R_StudioDrawPoints' inputs (ref/soft/r_studio.c:1802) */
