@@ -29,6 +29,7 @@ struct Emu
 	std::vector<int32_t> sintable, sedgepartner; std::vector<float> sedgeverts;
 	std::vector<uint16_t> alphamap; std::vector<uint8_t> addmap, modmap;
 	std::vector<rc_item_t> items; std::vector<rc_corner_t> corners; std::vector<rc_sortent_t> sortents;
+	std::vector<rc_bent_t> bents;
 	std::vector<uint8_t> sstatic; std::vector<rc_spart_t> parts; std::vector<float> bones, blight, mvpos; std::vector<int32_t> mlight;
 	int32_t styles[256];
 	struct Key { int32_t texnum; int32_t light[4]; bool valid; };
@@ -367,19 +368,24 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 		std::vector<uint32_t> nodevis(( sc->numnodes + 31 ) / 32 + 1 ), leafmark(( sc->numleafs + 31 ) / 32 + 1 ), surfmark(( sc->numsurfaces + 31 ) / 32 + 1 );
 		rc_mark_leaves( sc, vis.data(), nodevis.data(), leafmark.data());
 		/* A2 */
-		std::vector<rc_cand_t> cands( sc->numsurfaces + 1 );
+		int32_t maxc = sc->numsurfaces;
+		for( const rc_bent_t &b : E.bents ) maxc += b.numfaces * 64;
+		std::vector<rc_cand_t> cands( maxc + 1 );
+		std::vector<int32_t> leafbase( sc->numleafs + 1, -1 );
 		int32_t overflow = 0;
-		int ncands = rc_walk_world( sc, vw, nodevis.data(), leafmark.data(), surfmark.data(), stack.data(), stack_ints, cands.data(), sc->numsurfaces, &overflow );
+		int ncands = rc_walk_world( sc, vw, nodevis.data(), leafmark.data(), surfmark.data(), stack.data(), stack_ints, cands.data(), maxc, &overflow,
+			E.bents.data(), (int32_t)E.bents.size(), leafbase.data());
 		if( overflow ) E.counters[RC_CTR_OVERFLOW_STACK]++;
 		E.counters[RC_CTR_CANDS] += ncands;
 		/* A3 + A5 */
 		std::vector<rc_surf_t> surfs( ncands + 1 );
 		std::vector<uint16_t> candof( sc->numsurfaces + 2, 0 );
-		for( int ci = 0; ci < ncands; ci++ ) candof[cands[ci].surf] = (uint16_t)( ci + 1 );
+		for( int ci = 0; ci < ncands; ci++ ) if( cands[ci].surf >= 0 ) candof[cands[ci].surf] = (uint16_t)( ci + 1 );
 		std::vector<rc_edge_t> edges;
 		std::vector<rc_facerec_t> recs( ncands + 1 );
 		for( int ci = 0; ci < ncands; ci++ )
 		{
+			if( cands[ci].surf < 0 ) { memset( &surfs[ci], 0, sizeof( rc_surf_t )); memset( &recs[ci], 0, sizeof( rc_facerec_t )); continue; } /* a brush entity's slot */
 			/* as the kernels do it: k_faces begins every face and leaves its record; a face that has to inherit a clip
 			 * point is finished afterwards (k_faces_fix) - the record of such a face keeps what its edge loop wrote */
 			rc_edge_t local[256];
@@ -409,6 +415,41 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 					build_block( cands[ci].surf, surfs[ci].miplevel );
 			}
 		}
+		/* A13: the opaque brush entities, face by face (k_bmodels) */
+		if( !E.bents.empty())
+		{
+			std::vector<rc_edge_t> bedges( 64 * 1024 );
+			int32_t nbe = 0;
+			rc_bmout_t out;
+			out.surfs = surfs.data(); out.max_cands = ncands;
+			out.edges = bedges.data(); out.max_edges = (int32_t)bedges.size(); out.nedges = &nbe;
+			out.leafbase = leafbase.data(); out.candof = candof.data(); out.cache_need = nullptr;
+			out.nsurfs = 0; out.overflow = 0; out.noutmax = 0;
+			for( size_t e = 0; e < E.bents.size(); e++ )
+			{
+				const rc_bent_t *be = &E.bents[e];
+				const int32_t clipflags = rc_bmodel_check_bbox( vw, be->minmaxs );
+				if( clipflags < 0 ) continue;
+				const int32_t topnode = rc_find_topnode( sc, nodevis.data(), leafmark.data(), be->minmaxs );
+				if( topnode == RC_TOPNODE_NONE ) continue;
+				rc_view_t bv;
+				rc_bmodel_view( vw, be, &bv );
+				for( int f = 0; f < be->numfaces; f++ )
+					rc_bmodel_face( sc, &bv, E.bents.data(), (int32_t)E.bents.size(), (int32_t)e, be->firstface + f, clipflags, topnode,
+						nodevis.data(), leafmark.data(), &out );
+			}
+			for( int32_t k = 0; k < nbe && k < (int32_t)bedges.size(); k++ ) edges.push_back( bedges[k] );
+			E.counters[RC_CTR_BMODEL_SURFS] += out.nsurfs; E.counters[RC_CTR_SURFS] += out.nsurfs;
+			if( out.overflow ) E.counters[RC_CTR_OVERFLOW_BMODEL]++;
+			for( int ci = 0; ci < ncands; ci++ )
+				if( cands[ci].surf < 0 && surfs[ci].emitted )
+				{
+					const int32_t face = surfs[ci].surf;
+					const rc_surface_t *sf = &E.surfaces[face];
+					if( !( sf->flags & ( RC_SURF_DRAWSKY | RC_SURF_DRAWTURB )) && sf->cache_ofs[surfs[ci].miplevel] >= 0 && block_stale( face, surfs[ci].miplevel ))
+						build_block( face, surfs[ci].miplevel );
+				}
+		}
 		E.counters[RC_CTR_EDGES] += edges.size();
 		/* A4 + A9..A11 per scanline */
 		const int32_t *turb = E.sintable.data() + vw->turb_phase;
@@ -425,7 +466,7 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 			std::sort( ev.begin(), ev.end(), []( const rc_event_t &a, const rc_event_t &b ) { return rc_event_key( a.u, a.surfs ) < rc_event_key( b.u, b.surfs ); } );
 			int32_t ovf = 0;
 			int ns = rc_generate_spans( ev.data(), (int)ev.size(), head_iu, tail_u, stk.data(), cnt.data(), ncands + 1, neg.data(), 64,
-				spans.data(), (int)spans.size(), &ovf );
+				spans.data(), (int)spans.size(), &ovf, E.bents.empty() ? nullptr : surfs.data(), y );
 			{
 				/* the bit-set formulation the scanline kernel uses must give the same spans */
 				std::vector<uint32_t> bits(( ncands + 32 ) / 32 + 1, 0u );
@@ -498,6 +539,7 @@ int rc_dev_set_dlights( const rc_dlight_t *, int n ) { return n ? -1 : 0; }
 
 /* the display tail is not part of the debug harness (it keeps no frames) */
 int rc_dev_set_screenmap( const uint32_t *, int ) { return 0; }
+int rc_dev_set_bents( const rc_bent_t *bents, int n ) { E.bents.assign( bents, bents + ( n > 0 ? n : 0 )); return 0; }
 int rc_dev_draw2d( const rc_cmd2d_t *, int, int ) { snprintf( E.err, sizeof( E.err ), "HUD pass: not in the debug harness" ); return -1; }
 int rc_dev_blit( int, int, void *, size_t, float * ) { snprintf( E.err, sizeof( E.err ), "display tail: not in the debug harness" ); return -1; }
 

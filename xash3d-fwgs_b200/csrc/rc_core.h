@@ -203,8 +203,13 @@ RC_HD double rc_node_dot( const rc_view_t *vw, const rc_plane_t *pl )
  * index is the key here (a strictly monotone relabelling).
  * stack entry = 2 ints: node ref, (clipflags | stage << 4).
  */
+RC_HD int32_t rc_leaf_bmodel_slots( const rc_leaf_t *lf, const rc_bent_t *bents, int32_t nbents, int32_t upto );
+
+/* bents / leafbase (optional): every visited leaf reserves the surface slots of the brush entities that touch it, at its
+ * place in the order (= its key, LEAF_KEY r_bsp.c:541); leafbase[leaf] = the first of them (the caller presets -1) */
 RC_HD int32_t rc_walk_world( const rc_scene_t *sc, const rc_view_t *vw, const uint32_t *nodevis, const uint32_t *leafmark,
-	uint32_t *surfmark, int32_t *stack, int32_t stack_ints, rc_cand_t *cands, int32_t max_cands, int32_t *overflow )
+	uint32_t *surfmark, int32_t *stack, int32_t stack_ints, rc_cand_t *cands, int32_t max_cands, int32_t *overflow,
+	const rc_bent_t *bents, int32_t nbents, int32_t *leafbase )
 {
 	int32_t ncands = 0, sp = 0;
 	stack[sp++] = sc->headnode; stack[sp++] = 15;
@@ -260,6 +265,16 @@ RC_HD int32_t rc_walk_world( const rc_scene_t *sc, const rc_view_t *vw, const ui
 				continue;
 			for( int32_t m = leaf->firstmark; m < leaf->firstmark + leaf->nummark; m++ )
 				rc_setbit( surfmark, sc->marksurfaces[m] );
+			if( nbents && leafbase )
+			{
+				const int32_t n = rc_leaf_bmodel_slots( leaf, bents, nbents, nbents );
+				leafbase[li] = ncands;
+				for( int32_t k = 0; k < n; k++ )
+				{
+					if( ncands < max_cands ) { cands[ncands].surf = -1; cands[ncands].clipflags = 0; ncands++; }
+					else *overflow = 1;
+				}
+			}
 			continue;
 		}
 
@@ -782,6 +797,351 @@ RC_HD void rc_face_finish( const rc_scene_t *sc, const rc_view_t *vw, const rc_c
 }
 
 /* ------------------------------------------------------------------------------------------ */
+/* A13: opaque brush entities - R_DrawBEntitiesOnList (ref/soft/r_main.c:781), R_RotateBmodel,  */
+/* R_RecursiveClipBPoly, R_DrawSolidClippedSubmodelPolygons, R_DrawSubmodelPolygons             */
+/* (r_bsp.c:97-451), R_RenderBmodelFace (r_rast.c:596)                                          */
+
+#if defined( __CUDA_ARCH__ )
+#define RC_FETCH_ADD( p, n ) atomicAdd(( p ), ( n ))
+#define RC_ATOMIC_OR( p, v ) atomicOr(( p ), ( v ))
+#else
+#define RC_ATOMIC_OR( p, v ) ( *( p ) |= ( v ))
+static inline int32_t rc_fetch_add_host( int32_t *p, int32_t n ) { const int32_t o = *p; *p += n; return o; }
+#define RC_FETCH_ADD( p, n ) rc_fetch_add_host(( p ), ( n ))
+#endif
+
+#define RC_TOPNODE_NONE    ((int32_t)0x80000000 )
+#define RC_BACKFACE_EPSILON 0.01f
+#define RC_BM_MAXVERTS 56  /* per face: its own vertices + the points the BSP planes cut (the reference: 1000 per face) */
+#define RC_BM_MAXEDGES 112
+#define RC_BM_STACK    48
+#define RC_BM_FRAGEDGES 24 /* edges one fragment can emit: its polygon's + the left re-entry edge */
+
+/* R_BmodelCheckBBox, r_main.c:640: -1 = BMODEL_FULLY_CLIPPED, else the planes the box crosses */
+RC_HD int32_t rc_bmodel_check_bbox( const rc_view_t *vw, const float *minmaxs )
+{
+	int32_t clipflags = 0;
+	for( int i = 0; i < 4; i++ )
+	{
+		const int32_t *pindex = vw->frustum_idx[i];
+		float pt[3];
+		pt[0] = minmaxs[pindex[0]]; pt[1] = minmaxs[pindex[1]]; pt[2] = minmaxs[pindex[2]];
+		float d = rc_dot3( pt, vw->clip_normal[i] );
+		d -= vw->clip_dist[i];
+		if( d <= 0 )
+			return -1;
+		pt[0] = minmaxs[pindex[3]]; pt[1] = minmaxs[pindex[4]]; pt[2] = minmaxs[pindex[5]];
+		d = rc_dot3( pt, vw->clip_normal[i] );
+		d -= vw->clip_dist[i];
+		if( d <= 0 )
+			clipflags |= 1 << i;
+	}
+	return clipflags;
+}
+
+/* BOX_ON_PLANE_SIDE / BoxOnPlaneSide, public/xash3d_mathlib.h:197, xash3d_mathlib.c:368 */
+RC_HD int rc_box_on_plane_side( const float *emins, const float *emaxs, const rc_plane_t *p )
+{
+	if( p->type < 3 )
+	{
+		if( p->dist <= emins[p->type] ) return 1;
+		if( p->dist >= emaxs[p->type] ) return 2;
+		return 3;
+	}
+	/* dist1: the corner furthest along the normal, dist2: the opposite one (the signbits switch) */
+	float a[3], b[3];
+	for( int k = 0; k < 3; k++ )
+	{
+		const int neg = p->normal[k] < 0;
+		a[k] = neg ? emins[k] : emaxs[k];
+		b[k] = neg ? emaxs[k] : emins[k];
+	}
+	const float dist1 = p->normal[0] * a[0] + p->normal[1] * a[1] + p->normal[2] * a[2];
+	const float dist2 = p->normal[0] * b[0] + p->normal[1] * b[1] + p->normal[2] * b[2];
+	int sides = 0;
+	if( dist1 >= p->dist ) sides = 1;
+	if( dist2 < p->dist ) sides |= 2;
+	return sides;
+}
+
+/* R_FindTopnode, r_main.c:684: a node index, -1 - leaf for a non-solid leaf, RC_TOPNODE_NONE for "not visible" */
+RC_HD int32_t rc_find_topnode( const rc_scene_t *sc, const uint32_t *nodevis, const uint32_t *leafvis, const float *minmaxs )
+{
+	int32_t node = sc->headnode;
+	for( ;; )
+	{
+		if( node < 0 )
+		{
+			const int32_t leaf = -1 - node;
+			if( !rc_testbit( leafvis, leaf ))
+				return RC_TOPNODE_NONE;
+			return sc->leafs[leaf].contents != -2 /* CONTENTS_SOLID */ ? node : RC_TOPNODE_NONE;
+		}
+		if( !rc_testbit( nodevis, node ))
+			return RC_TOPNODE_NONE;
+		const int sides = rc_box_on_plane_side( minmaxs, minmaxs + 3, &sc->planes[sc->nodes[node].plane] );
+		if( sides == 3 )
+			return node;
+		node = ( sides & 1 ) ? sc->nodes[node].child[0] : sc->nodes[node].child[1];
+	}
+}
+
+/* R_EntityRotate, r_bsp.c:81 */
+RC_HD void rc_entity_rotate( const rc_bent_t *be, const float *in, float *out )
+{
+	out[0] = rc_dot3( be->rot[0], in );
+	out[1] = rc_dot3( be->rot[1], in );
+	out[2] = rc_dot3( be->rot[2], in );
+}
+
+/* the view as a brush entity's faces see it: modelorg = vieworigin - r_entorigin, then R_RotateBmodel (modelorg and the view
+ * vectors through entity_rotation, R_TransformFrustum again).  transformed_modelorg is D_SolidSurf's (r_edge.c:1003): the
+ * unrotated difference through the BASE view vectors. */
+RC_HD void rc_bmodel_view( const rc_view_t *vw, const rc_bent_t *be, rc_view_t *bv )
+{
+	*bv = *vw;
+	float mo[3];
+	mo[0] = vw->origin[0] - be->origin[0]; mo[1] = vw->origin[1] - be->origin[1]; mo[2] = vw->origin[2] - be->origin[2];
+	rc_transform( vw, mo, bv->modelorg_t );
+	rc_entity_rotate( be, mo, bv->origin );
+	rc_entity_rotate( be, vw->vforward, bv->vforward );
+	rc_entity_rotate( be, vw->vright, bv->vright );
+	rc_entity_rotate( be, vw->vup, bv->vup );
+	for( int i = 0; i < 4; i++ )
+	{
+		float v[3], v2[3];
+		v[0] = vw->screenedge[i][2]; v[1] = -vw->screenedge[i][0]; v[2] = vw->screenedge[i][1];
+		v2[0] = v[1] * bv->vright[0] + v[2] * bv->vup[0] + v[0] * bv->vforward[0];
+		v2[1] = v[1] * bv->vright[1] + v[2] * bv->vup[1] + v[0] * bv->vforward[1];
+		v2[2] = v[1] * bv->vright[2] + v[2] * bv->vup[2] + v[0] * bv->vforward[2];
+		bv->clip_normal[i][0] = v2[0]; bv->clip_normal[i][1] = v2[1]; bv->clip_normal[i][2] = v2[2];
+		bv->clip_dist[i] = rc_dot3( bv->origin, v2 );
+	}
+}
+
+/* does the entity's box touch the leaf's?  k_viswalk reserves surface slots (= the leaf's key) for every entity that does */
+RC_HD int rc_bent_touches_leaf( const rc_bent_t *be, const rc_leaf_t *lf )
+{
+	for( int k = 0; k < 3; k++ )
+		if( be->minmaxs[k] > lf->minmaxs[3 + k] || be->minmaxs[3 + k] < lf->minmaxs[k] )
+			return 0;
+	return 1;
+}
+
+/* surface slots a visited leaf needs: the faces of every brush entity whose box touches it */
+RC_HD int32_t rc_leaf_bmodel_slots( const rc_leaf_t *lf, const rc_bent_t *bents, int32_t nbents, int32_t upto )
+{
+	int32_t n = 0;
+	for( int32_t e = 0; e < nbents && e < upto; e++ )
+		if( rc_bent_touches_leaf( &bents[e], lf ))
+			n += bents[e].numfaces;
+	return n;
+}
+
+typedef struct { int16_t v0, v1, next; } rc_bedge_t;
+
+/* where a brush entity's fragments go: the view's surface and edge arrays */
+typedef struct
+{
+	rc_surf_t *surfs; int32_t max_cands;
+	rc_edge_t *edges; int32_t max_edges; int32_t *nedges;
+	const int32_t *leafbase;  /* [numleafs] first reserved slot of every visited leaf, -1 = not visited */
+	const uint16_t *candof;
+	uint32_t *cache_need;     /* (face, mip) blocks the batch samples (device); NULL: the caller derives them from the surfaces */
+	int32_t nsurfs, overflow, noutmax;
+} rc_bmout_t;
+
+/* post one fragment (or whole face): surface record into its slot, edges appended to the view's list */
+RC_HD void rc_bmodel_post( const rc_scene_t *sc, const rc_view_t *bv, const rc_cand_t *cand, rc_facestate_t *fs, int mkleft, int mkright,
+	int32_t slot, int32_t subkey, rc_bmout_t *out )
+{
+	rc_surf_t o;
+	rc_face_finish( sc, bv, cand, fs, mkleft, mkright, &o );
+	if( !o.emitted )
+		return;
+	if( fs->nout > fs->maxout ) { out->overflow = 1; return; }
+	o.emitted = 1 | ( subkey << 8 );
+	const int32_t at = RC_FETCH_ADD( out->nedges, fs->nout );
+	if( at + fs->nout > out->noutmax ) out->noutmax = at + fs->nout;
+	if( at + fs->nout <= out->max_edges )
+		for( int32_t k = 0; k < fs->nout; k++ ) out->edges[at + k] = fs->out[k];
+	out->surfs[slot] = o;
+	out->nsurfs++;
+	if( out->cache_need && !( o.flags & ( RC_SURF_DRAWSKY | RC_SURF_DRAWTURB )) && o.cache_ofs >= 0 )
+	{
+		const int32_t cs = cand->surf * 4 + o.miplevel;
+		RC_ATOMIC_OR( &out->cache_need[cs >> 5], 1u << ( cs & 31 ));
+	}
+}
+
+RC_HD void rc_bm_fs_init( rc_facestate_t *fs, rc_edge_t *buf, int32_t slot )
+{
+	fs->emitted = 0; fs->nearzi = 0; fs->nearzionly = 0; fs->lastvertvalid = 0; fs->wrote = 0;
+	fs->leftclipped = fs->rightclipped = 0;
+	fs->u1 = fs->v1 = fs->lzi1 = 0; fs->ceilv1 = 0;
+	for( int k = 0; k < 3; k++ ) fs->leftexit[k] = fs->leftenter[k] = fs->rightexit[k] = fs->rightenter[k] = 0.0f;
+	fs->out = buf; fs->nout = 0; fs->maxout = RC_BM_FRAGEDGES; fs->surfnum = (uint32_t)( slot + 1 );
+}
+
+/*
+ * One face of one brush entity in one view.  topnode: rc_find_topnode's answer for the entity.
+ *   a leaf:  R_DrawSubmodelPolygons - the face goes through R_RenderFace as a world face does (no edge cache: insubmodel)
+ *   a node:  R_DrawSolidClippedSubmodelPolygons - the face's edge loop is cut by the BSP planes below topnode
+ *            (R_RecursiveClipBPoly); every piece that ends in a visible non-solid leaf is posted (R_RenderBmodelFace)
+ * All pieces in one leaf carry that leaf's key (subkey = its first reserved slot + 1): the span stage sorts them among the
+ * world's surfaces by it, and among themselves by 1/z.
+ */
+RC_HD void rc_bmodel_face( const rc_scene_t *sc, const rc_view_t *bv, const rc_bent_t *bents, int32_t nbents, int32_t ent, int32_t face,
+	int32_t clipflags, int32_t topnode, const uint32_t *nodevis, const uint32_t *leafvis, rc_bmout_t *out )
+{
+	const rc_bent_t *be = &bents[ent];
+	const rc_surface_t *sf = &sc->surfaces[face];
+	const rc_plane_t *pl = &sc->planes[sf->plane];
+	const float dot = rc_dot3( bv->origin, pl->normal ) - pl->dist;
+	const int back = ( sf->flags & RC_SURF_PLANEBACK ) != 0;
+	rc_edge_t ebuf[RC_BM_FRAGEDGES];
+	rc_facestate_t fs;
+	rc_cand_t cand;
+	cand.surf = face; cand.clipflags = clipflags;
+
+	if( topnode < 0 )
+	{
+		if( !(( back && dot < -RC_BACKFACE_EPSILON ) || ( !back && dot > RC_BACKFACE_EPSILON )))
+			return;
+		const int32_t leaf = -1 - topnode;
+		const int32_t base = out->leafbase[leaf];
+		if( base < 0 )
+			return; /* the walk never reached the leaf (outside the frustum): nothing of it can be on screen */
+		const int32_t slot = base + rc_leaf_bmodel_slots( &sc->leafs[leaf], bents, nbents, ent ) + ( face - be->firstface );
+		if( slot >= out->max_cands ) { out->overflow = 1; return; }
+		int mkl, mkr;
+		rc_bm_fs_init( &fs, ebuf, slot );
+		rc_face_edges( sc, bv, &cand, out->candof, 0, &fs, &mkl, &mkr );
+		rc_bmodel_post( sc, bv, &cand, &fs, mkl, mkr, slot, base + 1, out );
+		return;
+	}
+
+	if(( !back && dot < -RC_BACKFACE_EPSILON ) || ( back && dot > RC_BACKFACE_EPSILON ))
+		return;
+
+	float verts[RC_BM_MAXVERTS][3];
+	rc_bedge_t edges[RC_BM_MAXEDGES];
+	int32_t stk_node[RC_BM_STACK]; int16_t stk_head[RC_BM_STACK];
+	int32_t numbverts = 0, numbedges = 0, sp = 0;
+	int16_t pfrontenter = 0, pfrontexit = 0;
+
+	/* the face's edge loop, clockwise: vertex i -> i + 1 */
+	if( sf->numedges > RC_BM_MAXVERTS / 2 || sf->numedges < 1 ) { out->overflow = 1; return; }
+	const float *sv = sc->sedgeverts + (size_t)sf->firstedge * 6;
+	for( int32_t j = 0; j < sf->numedges; j++ )
+	{
+		verts[numbverts][0] = sv[j * 6]; verts[numbverts][1] = sv[j * 6 + 1]; verts[numbverts][2] = sv[j * 6 + 2];
+		edges[j].v0 = (int16_t)numbverts;
+		edges[j].v1 = (int16_t)(( j + 1 < sf->numedges ) ? numbverts + 1 : 0 );
+		edges[j].next = (int16_t)(( j + 1 < sf->numedges ) ? j + 1 : -1 );
+		numbverts++;
+	}
+	numbedges = sf->numedges;
+	stk_node[0] = topnode; stk_head[0] = 0; sp = 1;
+
+	int planes[4], nplanes = 0;
+	for( int i = 0; i < 4; i++ )
+		if( clipflags & ( 1 << i ))
+			planes[nplanes++] = i;
+
+	while( sp > 0 )
+	{
+		sp--;
+		const int32_t node = stk_node[sp];
+		int16_t pedges = stk_head[sp];
+		if( node < 0 )
+		{
+			/* a leaf: draw if it is visible and not solid */
+			const int32_t leaf = -1 - node;
+			if( !rc_testbit( leafvis, leaf ) || sc->leafs[leaf].contents == -2 )
+				continue;
+			const int32_t base = out->leafbase[leaf];
+			if( base < 0 )
+				continue;
+			const int32_t slot = base + rc_leaf_bmodel_slots( &sc->leafs[leaf], bents, nbents, ent ) + ( face - be->firstface );
+			if( slot >= out->max_cands ) { out->overflow = 1; continue; }
+			/* R_RenderBmodelFace */
+			int mkl = 0, mkr = 0;
+			rc_bm_fs_init( &fs, ebuf, slot );
+			for( ; pedges >= 0; pedges = edges[pedges].next )
+			{
+				fs.leftclipped = fs.rightclipped = 0;
+				rc_clip_edge( bv, &fs, verts[edges[pedges].v0], verts[edges[pedges].v1], planes, nplanes, 0 );
+				if( fs.leftclipped ) mkl = 1;
+				if( fs.rightclipped ) mkr = 1;
+			}
+			rc_bmodel_post( sc, bv, &cand, &fs, mkl, mkr, slot, base + 1, out );
+			continue;
+		}
+		if( !rc_testbit( nodevis, node ))
+			continue;
+
+		/* R_RecursiveClipBPoly: the BSP plane in model space */
+		const rc_plane_t *sp_ = &sc->planes[sc->nodes[node].plane];
+		float tn[3];
+		const float tdist = sp_->dist - rc_dot3( be->origin, sp_->normal );
+		tn[0] = rc_dot3( be->rot[0], sp_->normal ); tn[1] = rc_dot3( be->rot[1], sp_->normal ); tn[2] = rc_dot3( be->rot[2], sp_->normal );
+		int16_t side_head[2] = { -1, -1 };
+		int makeclippededge = 0, abandoned = 0;
+		while( pedges >= 0 )
+		{
+			const int16_t pnext = edges[pedges].next;
+			const int16_t iv0 = edges[pedges].v0, iv1 = edges[pedges].v1;
+			const float lastdist = rc_dot3( verts[iv0], tn ) - tdist;
+			const int lastside = lastdist > 0 ? 0 : 1;
+			const float dist = rc_dot3( verts[iv1], tn ) - tdist;
+			const int side = dist > 0 ? 0 : 1;
+			if( side != lastside )
+			{
+				if( numbverts >= RC_BM_MAXVERTS || numbedges >= RC_BM_MAXEDGES - 1 ) { out->overflow = 1; abandoned = 1; break; }
+				const float frac = lastdist / ( lastdist - dist );
+				const int16_t pt = (int16_t)numbverts++;
+				verts[pt][0] = verts[iv0][0] + frac * ( verts[iv1][0] - verts[iv0][0] );
+				verts[pt][1] = verts[iv0][1] + frac * ( verts[iv1][1] - verts[iv0][1] );
+				verts[pt][2] = verts[iv0][2] + frac * ( verts[iv1][2] - verts[iv0][2] );
+				rc_bedge_t *e1 = &edges[numbedges];
+				e1->next = side_head[lastside]; side_head[lastside] = (int16_t)numbedges; e1->v0 = iv0; e1->v1 = pt;
+				rc_bedge_t *e2 = &edges[numbedges + 1];
+				e2->next = side_head[side]; side_head[side] = (int16_t)( numbedges + 1 ); e2->v0 = pt; e2->v1 = iv1;
+				numbedges += 2;
+				if( side == 0 ) pfrontenter = pt; else pfrontexit = pt;
+				makeclippededge = 1;
+			}
+			else
+			{
+				edges[pedges].next = side_head[side];
+				side_head[side] = pedges;
+			}
+			pedges = pnext;
+		}
+		if( abandoned )
+			continue;
+		if( makeclippededge )
+		{
+			if( numbedges >= RC_BM_MAXEDGES - 2 ) { out->overflow = 1; continue; }
+			rc_bedge_t *e1 = &edges[numbedges];
+			e1->next = side_head[0]; side_head[0] = (int16_t)numbedges; e1->v0 = pfrontexit; e1->v1 = pfrontenter;
+			rc_bedge_t *e2 = &edges[numbedges + 1];
+			e2->next = side_head[1]; side_head[1] = (int16_t)( numbedges + 1 ); e2->v0 = pfrontenter; e2->v1 = pfrontexit;
+			numbedges += 2;
+		}
+		/* side 0 is handled before side 1: push it last */
+		for( int i = 1; i >= 0; i-- )
+		{
+			if( side_head[i] < 0 )
+				continue;
+			if( sp >= RC_BM_STACK ) { out->overflow = 1; continue; }
+			stk_node[sp] = sc->nodes[node].child[i]; stk_head[sp] = side_head[i]; sp++;
+		}
+	}
+}
+
+/* ------------------------------------------------------------------------------------------ */
 /* A4: span generation for one scanline (ref/soft/r_edge.c:360-583)                             */
 
 typedef struct { int32_t u; uint32_t surfs; } rc_event_t; /* an active edge at this scanline */
@@ -818,8 +1178,36 @@ RC_HD uint64_t rc_event_key( int32_t u, uint32_t surfs )
  * stk/cnt: scratch of stkcap entries; neg: scratch of 2*negcap ints.
  * Returns the number of spans written (spans of surf 0 = background are written too).
  */
+/* the key R_LeadingEdge compares: a world surface's own number; a brush entity's piece carries its leaf's (all pieces in a
+ * leaf share it: "all bmodels in a leaf share the same key", r_bsp.c:542) - the number of the leaf's first reserved slot */
+RC_HD int32_t rc_span_key( const rc_surf_t *surfs, int32_t s )
+{
+	const int32_t sub = surfs ? ( surfs[s - 1].emitted >> 8 ) : 0;
+	return sub ? sub : s;
+}
+
+/* "must be two bmodels in the same leaf; sort on 1/z" (R_LeadingEdge, r_edge.c:419-445,463-481): is the entering piece a
+ * in front of the active piece b at this edge? */
+RC_HD int rc_span_zi_in_front( const rc_surf_t *a, const rc_surf_t *b, int32_t u, int32_t y )
+{
+	const float fv = (float)y;
+	const float fu = (float)( u - 0xFFFFF ) * ( 1.0f / 0x100000 );
+	const float newzi = a->d_ziorigin + fv * a->d_zistepv + fu * a->d_zistepu;
+	const float newzibottom = newzi * 0.99f;
+	const float testzi = b->d_ziorigin + fv * b->d_zistepv + fu * b->d_zistepu;
+	if( newzibottom >= testzi )
+		return 1;
+	const float newzitop = newzi * 1.01f;
+	if( newzitop >= testzi && a->d_zistepu >= b->d_zistepu )
+		return 1;
+	return 0;
+}
+
+/* surfs / y: the view's surface records and the scanline - needed when brush entities are in the view (pieces that share
+ * a leaf key are ordered by 1/z where they meet); NULL when there are none */
 RC_HD int32_t rc_generate_spans( const rc_event_t *ev, int32_t nev, int32_t head_iu, int32_t tail_u,
-	int32_t *stk, int32_t *cnt, int32_t stkcap, int32_t *neg, int32_t negcap, rc_span_t *spans, int32_t maxspans, int32_t *overflow )
+	int32_t *stk, int32_t *cnt, int32_t stkcap, int32_t *neg, int32_t negcap, rc_span_t *spans, int32_t maxspans, int32_t *overflow,
+	const rc_surf_t *surfs, int32_t y )
 {
 	int32_t depth = 0, nneg = 0, nspans = 0;
 	int32_t top = 0, top_last_u = head_iu; /* surfaces[1].last_u = edge_head_u_shift20 */
@@ -873,8 +1261,40 @@ RC_HD int32_t rc_generate_spans( const rc_event_t *ev, int32_t nev, int32_t head
 				if( ++neg[2 * i + 1] == 0 ) { neg[2 * i] = neg[2 * ( nneg - 1 )]; neg[2 * i + 1] = neg[2 * ( nneg - 1 ) + 1]; nneg--; }
 				continue;
 			}
-			for( i = 0; i < depth; i++ ) if( stk[i] >= lead ) break;
-			if( i < depth && stk[i] == lead ) { cnt[i]++; continue; }
+			if( !surfs )
+			{
+				for( i = 0; i < depth; i++ ) if( stk[i] >= lead ) break;
+				if( i < depth && stk[i] == lead ) { cnt[i]++; continue; }
+			}
+			else
+			{
+				/* with brush entities the stack is ordered by (key, then as the 1/z tests placed the pieces) */
+				for( i = 0; i < depth; i++ ) if( stk[i] == lead ) break;
+				if( i < depth ) { cnt[i]++; continue; }
+				const int32_t ks = rc_span_key( surfs, lead );
+				const int insub = ks != lead || ( surfs[lead - 1].emitted >> 8 ) != 0;
+				i = 0;
+				if( depth > 0 )
+				{
+					const int32_t k2 = rc_span_key( surfs, stk[0] );
+					if( ks < k2 || ( insub && ks == k2 && rc_span_zi_in_front( &surfs[lead - 1], &surfs[stk[0] - 1], u, y )))
+						i = 0;
+					else
+					{
+						for( ;; )
+						{
+							do { i++; } while( i < depth && ks > rc_span_key( surfs, stk[i] ));
+							if( i < depth && ks == rc_span_key( surfs, stk[i] ))
+							{
+								if( !insub ) continue;
+								if( rc_span_zi_in_front( &surfs[lead - 1], &surfs[stk[i] - 1], u, y )) break;
+								continue;
+							}
+							break;
+						}
+					}
+				}
+			}
 			if( depth >= stkcap ) { *overflow = 1; continue; }
 			if( i == 0 )
 			{

@@ -30,6 +30,8 @@ int rc_dev_update_surface_texnums( const int32_t *texnum, int n );
 /* blend tables of R_BuildBlendMaps (ref/soft/r_glblit.c:411-520): alphamap[3 * 1024 * 256] u16, addmap / modmap[65536] u8 */
 int rc_dev_upload_blendluts( const uint16_t *alphamap, const uint8_t *addmap, const uint8_t *modmap );
 /* the entities of the next batches as ordered draw items (rc_shared.h); nitems = 0: none */
+/* the opaque brush entities of the next batches (R_DrawBEntitiesOnList); n = 0 clears them */
+int rc_dev_set_bents( const rc_bent_t *bents, int n );
 /* the HUD pass: the commands applied in order to frame `view` of the last batch (colour only) */
 int rc_dev_draw2d( const rc_cmd2d_t *cmds, int n, int view );
 int rc_dev_set_items( const rc_item_t *items, int nitems, const rc_corner_t *corners, int ncorners, const rc_sortent_t *sortents, int nsortents );

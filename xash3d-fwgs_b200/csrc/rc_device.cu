@@ -94,6 +94,10 @@ struct rc_work_t
 	int32_t   *big_list, *big_count; int32_t big_cap; /* triangles k_tris_fast hands to k_tris_fast_big: {view, key number} */
 	/* studio models (k_studio_points) */
 	const uint8_t *sstatic; const rc_spart_t *parts; const float *bones, *blight; float *mvpos; int32_t *mlight;
+	/* brush entities (k_bmodels) */
+	const rc_bent_t *bents; int32_t nbents; const int32_t *bfaces; int32_t nbfaces; /* bfaces: entity << 16 | face within it */
+	int32_t   *leafbase;                /* [nviews][numleafs] first reserved slot of a visited leaf, -1 = not visited */
+	uint32_t  *bmvis;                   /* [nviews][nodewords + leafwords] node / leaf visframe bits of the view */
 	int32_t   *partbox;                 /* [nparts][6] bounding box of the part's transformed vertices as ordered int keys */
 	uint8_t   *itemvis;                 /* [nviews][nitems] k_item_cull: 0 = no triangle of the item can be drawn in the view */
 };
@@ -168,8 +172,16 @@ __global__ void __launch_bounds__( FC_THREADS ) k_faces( rc_scene_t sc, rc_work_
 		return;
 	const rc_view_t *vw = &w.views[view];
 	const rc_cand_t cand = w.cands[(size_t)view * w.max_cands + ci];
-	const rc_surface_t *sf = &sc.surfaces[cand.surf];
 	rc_surf_t *out = &w.surfs[(size_t)view * w.max_cands + ci];
+	if( cand.surf < 0 )
+	{
+		/* a slot k_viswalk reserved for a brush entity's face in this leaf: k_bmodels fills it when a piece lands there */
+		out->emitted = 0; out->flags = 0; out->surf = -1;
+		w.facerecs[(size_t)view * w.max_cands + ci].wrote = 0; w.facerecs[(size_t)view * w.max_cands + ci].state = 0;
+		w.facewrote[(size_t)view * w.max_cands + ci] = 0;
+		return;
+	}
+	const rc_surface_t *sf = &sc.surfaces[cand.surf];
 
 	/* reserve the most this face can emit: one edge per surfedge + the left re-entry edge */
 	int32_t want = sf->numedges + 1;
@@ -211,6 +223,43 @@ __global__ void __launch_bounds__( FC_THREADS ) k_faces( rc_scene_t sc, rc_work_
 	rc_face_commit( sc, w, view, ci, &cand, &fs, ml, mr, out );
 	rc_face_store( &fs, ml, mr, 0, &recs[ci] );
 	w.facewrote[(size_t)view * w.max_cands + ci] = (uint8_t)fs.wrote;
+}
+
+/* opaque brush entities (rc_core.h A13): thread per (view, entity face).  Runs after k_faces / k_faces_fix: the pieces go
+ * into the slots k_viswalk reserved at their leaf's place in the surface order, their edges behind the world's */
+__global__ void __launch_bounds__( 64 ) k_bmodels( rc_scene_t sc, rc_work_t w )
+{
+	const int view = blockIdx.y;
+	const int32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+	if( g >= w.nbfaces )
+		return;
+	const int32_t ent = w.bfaces[g] >> 16, lf = w.bfaces[g] & 0xFFFF;
+	const rc_bent_t *be = &w.bents[ent];
+	const rc_view_t *vw = &w.views[view];
+	const int32_t clipflags = rc_bmodel_check_bbox( vw, be->minmaxs );
+	if( clipflags < 0 )
+		return;
+	const uint32_t *nodevis = w.bmvis + (size_t)view * ( w.nodewords + w.leafwords ), *leafvis = nodevis + w.nodewords;
+	const int32_t topnode = rc_find_topnode( &sc, nodevis, leafvis, be->minmaxs );
+	if( topnode == RC_TOPNODE_NONE )
+		return;
+	rc_view_t bv;
+	rc_bmodel_view( vw, be, &bv );
+	rc_bmout_t out;
+	out.surfs = w.surfs + (size_t)view * w.max_cands; out.max_cands = w.ncands[view];
+	out.edges = w.edges + (size_t)view * w.max_edges; out.max_edges = w.max_edges; out.nedges = &w.nedges[view];
+	out.leafbase = w.leafbase + (size_t)view * sc.numleafs;
+	out.candof = w.candof + (size_t)view * ( sc.numsurfaces + 2 );
+	out.cache_need = w.cache_need;
+	out.nsurfs = 0; out.overflow = 0; out.noutmax = 0;
+	rc_bmodel_face( &sc, &bv, w.bents, w.nbents, ent, be->firstface + lf, clipflags, topnode, nodevis, leafvis, &out );
+	if( out.nsurfs )
+	{
+		atomicAdd( &w.counters[RC_CTR_BMODEL_SURFS], (unsigned long long)out.nsurfs );
+		atomicAdd( &w.counters[RC_CTR_SURFS], (unsigned long long)out.nsurfs );
+	}
+	if( out.overflow ) atomicAdd( &w.counters[RC_CTR_OVERFLOW_BMODEL], 1ull );
+	if( out.noutmax > w.max_edges ) atomicAdd( &w.counters[RC_CTR_OVERFLOW_EDGES], 1ull );
 }
 
 /* the faces k_faces left waiting for an earlier face's clip point (a few per view): a warp per face - the lanes look at
@@ -619,6 +668,8 @@ struct Dev
 	int32_t *d_biglist = nullptr; size_t cap_big = 0;
 	rc_cmd2d_t *d_cmds2d = nullptr;
 	int32_t *d_pairs = nullptr; size_t cap_pairs = 0; int fast_maxcount = 0;
+	rc_bent_t *d_bents = nullptr; int32_t *d_bfaces = nullptr; int nbents = 0, nbfaces = 0;
+	int32_t *d_leafbase = nullptr; uint32_t *d_bmvis = nullptr; size_t cap_leafbase = 0, cap_bmvis = 0;
 	int32_t *d_partbox = nullptr; size_t cap_partbox = 0; uint8_t *d_itemvis = nullptr; size_t cap_itemvis = 0;
 	int32_t *d_item_order = nullptr; rc_poly_t *d_polys = nullptr;
 	size_t cap_item_order = 0, cap_polys = 0;
@@ -847,6 +898,9 @@ rc_work_t make_slice( int k, int v0, int v1 )
 	ws.big_cap = (int32_t)( D.cap_big / RC_MAX_SLICES ); ws.big_list = D.d_biglist ? D.d_biglist + (size_t)2 * ws.big_cap * k : nullptr;
 	ws.big_count = D.d_nlist + 16 * k + 8; ws.pair_count = D.d_nlist + 16 * k + 9;
 	ws.pairs = D.d_pairs ? D.d_pairs + (size_t)v0 * ( D.nfast_items > 0 ? D.nfast_items : 1 ) : nullptr;
+	ws.bents = D.d_bents; ws.nbents = D.nbents; ws.bfaces = D.d_bfaces; ws.nbfaces = D.nbfaces;
+	ws.leafbase = D.d_leafbase ? D.d_leafbase + (size_t)v0 * sc.numleafs : nullptr;
+	ws.bmvis = D.d_bmvis ? D.d_bmvis + (size_t)v0 * ( ws.nodewords + ws.leafwords ) : nullptr;
 	ws.partbox = D.d_partbox; ws.itemvis = D.d_itemvis ? D.d_itemvis + (size_t)v0 * D.nitems : nullptr;
 	ws.sstatic = D.d_sstatic; ws.parts = D.d_parts; ws.bones = D.d_bones; ws.blight = D.d_blight; ws.mvpos = D.d_mvpos; ws.mlight = D.d_mlight;
 	return ws;
@@ -872,6 +926,7 @@ int launch_slice( const rc_work_t &ws, int k, cudaStream_t st, cudaEvent_t *evs,
 	const rc_scene_t &sc = D.sc;
 	CK( cudaMemsetAsync( ws.cache_need, 0, sizeof( uint32_t ) * (( sc.numsurfaces * 4 + 31 ) / 32 + 1 ), st ));
 	CK( cudaMemsetAsync( ws.cache_nlist, 0, sizeof( int32_t ) * 16, st ));
+	if( D.nbents ) CK( cudaMemsetAsync( ws.leafbase, 0xFF, sizeof( int32_t ) * (size_t)ws.nviews * sc.numleafs, st ));
 	if( evs ) CK( cudaEventRecord( evs[0], st ));
 	k_viswalk<VW_NTHREADS><<<ws.nviews < D.vw_grid ? ws.nviews : D.vw_grid, VW_NTHREADS, (size_t)ws.vis_smem, st>>>( sc, ws );
 	D.launches++;
@@ -885,6 +940,12 @@ int launch_slice( const rc_work_t &ws, int k, cudaStream_t st, cudaEvent_t *evs,
 		KCHECK( "k_faces", st );
 		k_faces_fix<<<D.num_sms * 2, FC_THREADS, 0, st>>>( sc, ws ); D.launches++;
 		KCHECK( "k_faces_fix", st );
+		if( D.nbents && D.nbfaces )
+		{
+			dim3 gb(( D.nbfaces + 63 ) / 64, ws.nviews );
+			k_bmodels<<<gb, 64, 0, st>>>( sc, ws ); D.launches++;
+			KCHECK( "k_bmodels", st );
+		}
 	}
 	if( evs ) CK( cudaEventRecord( evs[2], st ));
 	{
@@ -1047,7 +1108,7 @@ void rc_dev_shutdown( void )
 	cudaDeviceSynchronize();
 	free_batch();
 	/* everything rc_dev_init / the uploads created, so that R_Shutdown + R_Init (vid_restart) starts clean */
-	void **ptrs[] = { (void **)&D.d_pairs, (void **)&D.d_partbox, (void **)&D.d_itemvis, (void **)&D.d_cmds2d, (void **)&D.d_trikeys, (void **)&D.d_biglist, (void **)&D.d_sstatic, (void **)&D.d_parts, (void **)&D.d_bones, (void **)&D.d_blight, (void **)&D.d_mvpos, (void **)&D.d_mlight, (void **)&D.d_item_order, (void **)&D.d_polys, (void **)&D.d_alphamap, (void **)&D.d_addmap, (void **)&D.d_modmap, (void **)&D.d_items, (void **)&D.d_corners, (void **)&D.d_sortents, (void **)&D.d_display, (void **)&D.d_screenmap, (void **)&D.d_dlights, (void **)&D.d_dlightbits,
+	void **ptrs[] = { (void **)&D.d_bents, (void **)&D.d_bfaces, (void **)&D.d_leafbase, (void **)&D.d_bmvis, (void **)&D.d_pairs, (void **)&D.d_partbox, (void **)&D.d_itemvis, (void **)&D.d_cmds2d, (void **)&D.d_trikeys, (void **)&D.d_biglist, (void **)&D.d_sstatic, (void **)&D.d_parts, (void **)&D.d_bones, (void **)&D.d_blight, (void **)&D.d_mvpos, (void **)&D.d_mlight, (void **)&D.d_item_order, (void **)&D.d_polys, (void **)&D.d_alphamap, (void **)&D.d_addmap, (void **)&D.d_modmap, (void **)&D.d_items, (void **)&D.d_corners, (void **)&D.d_sortents, (void **)&D.d_display, (void **)&D.d_screenmap, (void **)&D.d_dlights, (void **)&D.d_dlightbits,
 		(void **)&D.d_colormap, (void **)&D.d_lightgamma, (void **)&D.d_sintable, (void **)&D.d_textures, (void **)&D.d_texels,
 		(void **)&D.d_styles, (void **)&D.d_keys, (void **)&D.d_need, (void **)&D.d_list, (void **)&D.d_nlist,
 		(void **)&D.d_counters, &D.d_flush };
@@ -1057,7 +1118,7 @@ void rc_dev_shutdown( void )
 	D.cap_cands = D.cap_edges = D.cap_blk_events = 0; D.caps_dirty = false;
 	D.nitems = D.ncorners = D.nsortents = 0; D.h_items.clear(); D.ntris = 0; D.cap_item_order = D.cap_polys = 0;
 	D.nparts = D.totalverts = D.totalnorms = 0; D.cap_mvpos = D.cap_mlight = 0; D.studio_dirty = false;
-	D.nfast_items = D.fast_tris = 0; D.cap_trikeys = D.cap_big = 0; D.cap_partbox = D.cap_itemvis = D.cap_pairs = 0;
+	D.nfast_items = D.fast_tris = 0; D.cap_trikeys = D.cap_big = 0; D.cap_partbox = D.cap_itemvis = D.cap_pairs = 0; D.nbents = D.nbfaces = 0; D.cap_leafbase = D.cap_bmvis = 0;
 	D.display_bytes = 0; D.ndlights = 0; D.screen_bpp = 0; D.cache_texels = 0; D.ntextures = 0;
 	D.sc = rc_scene_t{}; D.h_surfaces.clear(); D.h_textures.clear();
 	cudaStream_t *streams[] = { &D.stream, &D.copy };
@@ -1219,6 +1280,21 @@ int rc_dev_set_items( const rc_item_t *items, int nitems, const rc_corner_t *cor
 	return 0;
 }
 
+int rc_dev_set_bents( const rc_bent_t *bents, int n )
+{
+	if( n > RC_MAX_BENTS ) n = RC_MAX_BENTS;
+	D.nbents = 0; D.nbfaces = 0;
+	if( n <= 0 ) return 0;
+	std::vector<int32_t> bf;
+	for( int e = 0; e < n; e++ )
+		for( int f = 0; f < bents[e].numfaces && f < 65536; f++ ) bf.push_back(( e << 16 ) | f );
+	if( upload( &D.d_bents, bents, (size_t)n ) != 0 ) return -1;
+	if( upload( &D.d_bfaces, bf.data(), bf.size()) != 0 ) return -1;
+	D.h2d_bytes += sizeof( rc_bent_t ) * (size_t)n + 4 * bf.size();
+	D.nbents = n; D.nbfaces = (int)bf.size();
+	return 0;
+}
+
 int rc_dev_draw2d( const rc_cmd2d_t *cmds, int n, int view )
 {
 	if( !D.have_batch || view < 0 || view >= D.w.nviews ) { snprintf( D.err, sizeof( D.err ), "rc_dev_draw2d: no such frame" ); return -1; }
@@ -1321,6 +1397,12 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 	for( int attempt = 0; ; attempt++ )
 	{
 		if( ensure_batch( nviews, width, height ) != 0 ) return -1;
+		if( D.nbents )
+		{
+			const size_t need_l = (size_t)D.cap_views * D.sc.numleafs, need_b = (size_t)D.cap_views * ( D.w.nodewords + D.w.leafwords );
+			if( need_l > D.cap_leafbase ) { if( dalloc( &D.d_leafbase, need_l ) != 0 ) return -1; D.cap_leafbase = need_l; }
+			if( need_b > D.cap_bmvis ) { if( dalloc( &D.d_bmvis, need_b ) != 0 ) return -1; D.cap_bmvis = need_b; }
+		}
 		if( D.nitems && D.ntris )
 		{
 			const size_t need_v = (size_t)D.cap_views * D.nitems;

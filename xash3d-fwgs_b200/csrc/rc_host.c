@@ -774,6 +774,8 @@ static void rc_setup_view( const ref_viewpass_t *rvp, rc_view_t *v )
 	screenedge[3][0] = 0; screenedge[3][1] = 1.0f / (( 1.0f - yOrigin ) * verticalFieldOfView ); screenedge[3][2] = 1;
 	for( int i = 0; i < 4; i++ )
 		VectorNormalize( screenedge[i] );
+	for( int i = 0; i < 4; i++ )
+		VectorCopy( screenedge[i], v->screenedge[i] );
 
 	/* R_TransformFrustum */
 	for( int i = 0; i < 4; i++ )
@@ -1310,7 +1312,6 @@ static void rc_build_items( void )
 	gEngfuncs.pfnDrawTransparentTriangles();
 	gEngfuncs.CL_DrawEFX( gp_cl->time - gp_cl->oldtime, true );
 	GL_SetRenderMode( kRenderNormal );
-	if( rc.num_edge && !rc.warned[4] ) { rc.warned[4] = true; gEngfuncs.Con_Reportf( "ref_cuda: opaque brush entities are not drawn yet\n" ); }
 
 	/* texture numbers -> texel arena offsets, triangle numbering */
 	int order = 0;
@@ -1905,6 +1906,74 @@ static void rc_add_studio( cl_entity_t *e )
 	}
 }
 
+/* ---------------------------------------------------------------------------------------------- */
+/* opaque brush entities: the per-entity, view-independent part of R_DrawBEntitiesOnList (ref/soft/r_main.c:781) - the
+ * rotated bounding box (RotatedBBox, :723) and the rotation matrix R_RotateBmodel builds (r_bsp.c:97-160, sin / cos on
+ * the host) - for the device, which clips every face to the view and to the world BSP per view (rc_core.h A13)           */
+
+static void rc_concat_rotations( float in1[3][3], float in2[3][3], float out[3][3] )
+{
+	for( int i = 0; i < 3; i++ )
+		for( int j = 0; j < 3; j++ )
+			out[i][j] = in1[i][0] * in2[0][j] + in1[i][1] * in2[1][j] + in1[i][2] * in2[2][j];
+}
+
+static void rc_build_bents( void )
+{
+	static rc_bent_t bents[RC_MAX_BENTS];
+	int n = 0;
+	for( int i = 0; i < rc.num_edge && n < RC_MAX_BENTS; i++ )
+	{
+		cl_entity_t *e = rc.edge_ents[i];
+		model_t *mod = e->model;
+		if( !mod || mod->nummodelsurfaces == 0 || mod->type != mod_brush )
+			continue;
+		rc_bent_t *b = &bents[n++];
+		memset( b, 0, sizeof( *b ));
+		/* RotatedBBox */
+		vec3_t tmins, tmaxs;
+		if( !e->angles[0] && !e->angles[1] && !e->angles[2] )
+		{
+			VectorCopy( mod->mins, tmins ); VectorCopy( mod->maxs, tmaxs );
+		}
+		else
+		{
+			vec3_t forward, right, up, tmp, v;
+			for( int k = 0; k < 3; k++ ) { tmins[k] = 99999; tmaxs[k] = -99999; }
+			AngleVectors( e->angles, forward, right, up );
+			for( int c = 0; c < 8; c++ )
+			{
+				tmp[0] = ( c & 1 ) ? mod->mins[0] : mod->maxs[0];
+				tmp[1] = ( c & 2 ) ? mod->mins[1] : mod->maxs[1];
+				tmp[2] = ( c & 4 ) ? mod->mins[2] : mod->maxs[2];
+				VectorScale( forward, tmp[0], v );
+				VectorMA( v, -tmp[1], right, v );
+				VectorMA( v, tmp[2], up, v );
+				for( int j = 0; j < 3; j++ )
+				{
+					if( v[j] < tmins[j] ) tmins[j] = v[j];
+					if( v[j] > tmaxs[j] ) tmaxs[j] = v[j];
+				}
+			}
+		}
+		VectorAdd( tmins, e->origin, b->minmaxs );
+		VectorAdd( tmaxs, e->origin, ( b->minmaxs + 3 ));
+		VectorCopy( e->origin, b->origin );
+		/* R_RotateBmodel: yaw, pitch, roll */
+		float angle, sn, cs, temp1[3][3], temp2[3][3], temp3[3][3];
+		angle = e->angles[YAW]; angle = angle * M_PI_F * 2 / 360.0f; sn = sin( angle ); cs = cos( angle );
+		temp1[0][0] = cs; temp1[0][1] = sn; temp1[0][2] = 0; temp1[1][0] = -sn; temp1[1][1] = cs; temp1[1][2] = 0; temp1[2][0] = 0; temp1[2][1] = 0; temp1[2][2] = 1;
+		angle = e->angles[PITCH]; angle = angle * M_PI_F * 2 / 360.0f; sn = sin( angle ); cs = cos( angle );
+		temp2[0][0] = cs; temp2[0][1] = 0; temp2[0][2] = -sn; temp2[1][0] = 0; temp2[1][1] = 1; temp2[1][2] = 0; temp2[2][0] = sn; temp2[2][1] = 0; temp2[2][2] = cs;
+		rc_concat_rotations( temp2, temp1, temp3 );
+		angle = e->angles[ROLL]; angle = angle * M_PI_F * 2 / 360.0f; sn = sin( angle ); cs = cos( angle );
+		temp1[0][0] = 1; temp1[0][1] = 0; temp1[0][2] = 0; temp1[1][0] = 0; temp1[1][1] = cs; temp1[1][2] = sn; temp1[2][0] = 0; temp1[2][1] = -sn; temp1[2][2] = cs;
+		rc_concat_rotations( temp1, temp3, b->rot );
+		b->firstface = mod->firstmodelsurface; b->numfaces = mod->nummodelsurfaces;
+	}
+	RC_CHECK_DEV( rc_dev_set_bents( bents, n ));
+}
+
 /* LightToTexGamma (ref/soft/r_local.h:518-523) reads the engine's live table, or nothing in linear gamma space */
 static void rc_resolve_lightgamma( void )
 {
@@ -1938,6 +2007,7 @@ static void rc_prepare_batch( void )
 	rc_resolve_texnums( false );
 	RC_CHECK_DEV( rc_dev_set_lightstyles( rc.lightstylevalue ));
 	rc_push_dlights();
+	rc_build_bents();
 	rc_build_items();
 }
 

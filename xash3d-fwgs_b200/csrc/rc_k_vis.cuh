@@ -434,6 +434,18 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 	const int32_t nseq = nlvl ? e_size[0] : 0;
 	for( int32_t i = t; i < nseq; i += VW_THREADS ) seq[i] = 0;
 	__syncthreads();
+	/* brush entities: a visited leaf's place in the sequence is its key (LEAF_KEY, r_bsp.c:541); it reserves a surface slot
+	 * there for every face of every entity whose box touches the leaf - k_bmodels posts the face pieces into them */
+	if( w.nbents )
+	{
+		const int32_t nleaf = s_nleaf;
+		for( int32_t k = t; k < nleaf; k += VW_THREADS )
+		{
+			const int32_t e = leaflist[k];
+			const int32_t n = rc_leaf_bmodel_slots( &sc.leafs[-1 - e_ref[e]], w.bents, w.nbents, w.nbents );
+			if( n ) seq[e_pos[e]] = n;
+		}
+	}
 	/* thread per surface (a word of the mark set per thread would leave most of the block idle and walk up to 32
 	 * bits serially); a thread only ever changes its own bit */
 	for( int32_t s = t; s < sc.numsurfaces; s += VW_THREADS )
@@ -470,6 +482,21 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 	}
 	const int32_t total = carry;
 	rc_cand_t *cands = w.cands + (size_t)view * w.max_cands;
+	if( w.nbents )
+	{
+		const int32_t nleaf = s_nleaf;
+		int32_t *leafbase = w.leafbase + (size_t)view * sc.numleafs;
+		for( int32_t k = t; k < nleaf; k += VW_THREADS )
+		{
+			const int32_t e = leaflist[k], leaf = -1 - e_ref[e], pos = e_pos[e];
+			const int32_t base = seq[pos], n = ( pos + 1 < nseq ? seq[pos + 1] : total ) - base;
+			leafbase[leaf] = base;
+			for( int32_t o = base; o < base + n && o < w.max_cands; o++ ) { cands[o].surf = -1; cands[o].clipflags = 0; }
+		}
+		/* R_FindTopnode and R_RecursiveClipBPoly test node / leaf visframe: the PVS marks leave the block */
+		uint32_t *out = w.bmvis + (size_t)view * ( w.nodewords + w.leafwords );
+		for( int32_t i = t; i < w.nodewords + w.leafwords; i += VW_THREADS ) out[i] = nodevis[i]; /* leafmark follows nodevis */
+	}
 	uint16_t *candof = w.candof + (size_t)view * ( sc.numsurfaces + 2 );
 	for( int32_t s = t; s < sc.numsurfaces; s += VW_THREADS )
 	{

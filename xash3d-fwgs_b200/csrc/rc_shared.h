@@ -149,6 +149,7 @@ typedef struct
 	int32_t sky_color;           /* (int)sw_clearcolor & 0xFFFF */
 	int32_t flags;               /* ref_viewpass_t.flags */
 	float   pvs_radius;
+	float   screenedge[4][3];    /* qfrustum.screenedge normals (view space): R_TransformFrustum runs again per brush entity */
 	int32_t texfilt;             /* sw_texfilt == 1: D_DrawSpans16's texture dither (ref/soft/r_scan.c:503-672) */
 	float   aliastransform[3][4]; /* R_SetUpWorldTransform (ref/soft/r_trialias.c:52): world -> view space for R_SetupFinalVert */
 } rc_view_t;
@@ -226,6 +227,18 @@ typedef struct
 	int32_t pad[1];
 } rc_sortent_t; /* 32 B */
 
+/* an opaque brush entity of the batch (tr.draw_list->edge_entities, R_DrawBEntitiesOnList ref/soft/r_main.c:781): its
+ * faces join the view's edge list - keyed by the world leaf they lie in - and are drawn by the world's span stages */
+#define RC_MAX_BENTS 256
+typedef struct
+{
+	float   origin[3];       /* r_entorigin */
+	float   rot[3][3];       /* entity_rotation (R_RotateBmodel, r_bsp.c:97): yaw, pitch, roll matrices concatenated on the host */
+	float   minmaxs[6];      /* RotatedBBox + origin */
+	int32_t firstface, numfaces;
+	int32_t pad[2];
+} rc_bent_t; /* 92 B -> 96 */
+
 /* a 2-D draw of the frame's HUD pass (R_DrawStretchPic / Draw_Fill, ref/soft/r_draw.c:38,159), clipped on the host */
 enum { RC_2D_PIC = 0, RC_2D_FILL = 1 };
 typedef struct
@@ -301,7 +314,9 @@ enum
 	RC_CTR_OVERFLOW_STACK, RC_CTR_OVERFLOW_CANDS, RC_CTR_SERIAL_LINES, RC_CTR_SORTED_LINES, RC_CTR_UNSTAGED_BANDS,
 	RC_CTR_MAX_CANDS /* most faces one view listed */, RC_CTR_MAX_EDGES /* most edges one view emitted */, RC_CTR_MAX_BAND_EVENTS /* most event slots one band wanted */,
 	RC_CTR_OVERFLOW_CACHE /* (face, mip) blocks k_cache_build could not build */, RC_CTR_TRIS, RC_CTR_TRI_PIXELS, RC_CTR_WIDE_LINES /* scanlines k_lines_wide took */, RC_CTR_OVERFLOW_FIX, RC_CTR_FIXED_FACES,
-	RC_CTR_TRI_WRITTEN /* pixels k_tri_resolve shaded (the key path's visible fragments) */, RC_CTR_BIG_TRIS /* triangles k_tris_fast_big took */, RC_CTR_COUNT = 64 /* 16.. = debug-build phase clocks */
+	RC_CTR_TRI_WRITTEN /* pixels k_tri_resolve shaded (the key path's visible fragments) */, RC_CTR_BIG_TRIS /* triangles k_tris_fast_big took */,
+	RC_CTR_BMODEL_SURFS /* brush entity surfaces (face fragments) posted */, RC_CTR_BMODEL_TIES /* scanlines where two of them with one leaf key overlapped */,
+	RC_CTR_OVERFLOW_BMODEL /* a face whose BSP clipping outgrew the fragment scratch */, RC_CTR_COUNT = 64 /* 16.. = debug-build phase clocks */
 };
 
 #ifdef __cplusplus

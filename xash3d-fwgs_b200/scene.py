@@ -38,7 +38,7 @@ assert C.sizeof(RefViewpass) == 56
 
 CTR_NAMES = ["views", "pixels", "cands", "surfs", "edges", "spans", "cache_blocks", "cache_texels",
              "overflow_edges", "overflow_events", "overflow_stack", "overflow_cands", "serial_lines", "sorted_lines", "unstaged_bands",
-             "max_cands", "max_edges", "max_band_events", "overflow_cache", "tris", "tri_pixels", "wide_lines", "overflow_fix", "fixed_faces", "tri_written", "big_tris"]
+             "max_cands", "max_edges", "max_band_events", "overflow_cache", "tris", "tri_pixels", "wide_lines", "overflow_fix", "fixed_faces", "tri_written", "big_tris", "bmodel_surfs", "bmodel_ties", "overflow_bmodel"]
 
 
 @functools.lru_cache(maxsize=8)
@@ -315,6 +315,21 @@ def add_studio_models(r, cams, count=64, nbones=32, ahead=72.0, drop=56.0, mdl=N
         org = (c[0] + ahead * math.cos(yaw), c[1] + ahead * math.sin(yaw), c[2] - drop)
         r.add_entity(mi, org, angles=(0.0, 37.0 * k, 0.0), frame=(k * 3) % 30, framerate=1.0, animtime=animtime + 0.01 * (k % 16))
     return mi
+
+
+def add_brush_entities(r, m, cams, count=16, ahead=88.0, drop=24.0, rotate=True, rendermode=0, renderamt=255):
+    """brush entities (doors / crates): instances of the map's box submodels (make_map(..., brush_models=n)) `ahead` units
+    in front of the first `count` cameras; every second one turned about the vertical axis, every fifth tilted as well."""
+    models = m.extras["brush_models"]
+    cams = np.asarray(cams, dtype=np.float32).reshape(-1, 6)
+    for k in range(count):
+        c = cams[k % len(cams)]
+        yaw = math.radians(float(c[4]))
+        org = (c[0] + ahead * math.cos(yaw), c[1] + ahead * math.sin(yaw), c[2] - drop)
+        ang = (0.0, 0.0, 0.0)
+        if rotate and k % 2:
+            ang = (12.0 * (k % 5 == 0), 25.0 + 13.0 * k, 8.0 * (k % 5 == 0))
+        r.add_entity(models[k % len(models)]["modelindex"], org, angles=ang, rendermode=rendermode, renderamt=renderamt)
 
 
 def sprite_image(seed, w=64, h=64):

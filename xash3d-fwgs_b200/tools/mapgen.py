@@ -141,6 +141,7 @@ class MapSpec:
     ntextures: int = 16
     name: str = "synth"
     novis: bool = False  # no visibility lump: every leaf's visofs is -1
+    brush_models: int = 0  # box-shaped brush submodels "*1".."*n" (doors / crates for brush entities), centred on their own origin
 
 
 @dataclass
@@ -558,6 +559,57 @@ def generate(spec: MapSpec = MapSpec(), ncameras: int = 256) -> GeneratedMap:
                 light_blob += rgb.tobytes()
         face_recs.append((f["plane"], f["side"], first, 4, ti, styles, lightofs))
 
+    # ---- brush submodels: boxes around their own origin (the entity's origin places them), six outward faces each
+    nworldfaces = len(face_recs)
+    extra_planes = []  # (axis, dist) in model space, after the world's planes
+    submodels = []  # (mins, maxs, firstface, numfaces)
+    for mi in range(spec.brush_models):
+        half = (16 + 8 * (int(_hash_u32(np.int64(mi), np.int64(spec.seed + 11))) % 4),
+                16 + 8 * (int(_hash_u32(np.int64(mi), np.int64(spec.seed + 12))) % 4),
+                16 + 16 * (int(_hash_u32(np.int64(mi), np.int64(spec.seed + 13))) % 3))
+        first_face = len(face_recs)
+        for axis in range(3):
+            for side in (0, 1):
+                nsign = 1.0 if side == 0 else -1.0
+                pc = nsign * half[axis]
+                ua, va = [a for a in range(3) if a != axis]
+                n = np.zeros(3)
+                n[axis] = nsign
+                up = np.zeros(3)
+                up[va] = 1.0
+                right = np.cross(-n, up)
+                rs = right[ua]
+                rl, rr = (-half[ua], half[ua]) if rs > 0 else (half[ua], -half[ua])
+
+                def P(r, t, axis=axis, ua=ua, va=va, pc=pc):
+                    q = [0.0, 0.0, 0.0]
+                    q[axis], q[ua], q[va] = pc, r, t
+                    return ("m", mi, *q)  # keyed apart from the world's vertices
+
+                corners = [P(rl, half[va]), P(rr, half[va]), P(rr, -half[va]), P(rl, -half[va])]
+                miptex = (wall_texs if axis != 2 else floor_texs)[(mi + axis) % len(wall_texs if axis != 2 else floor_texs)]
+                ti = get_texinfo(axis, miptex, 0)
+                first = len(surfedges)
+                ids = [vid(c) for c in corners]
+                for q in range(4):
+                    surfedges.append(eid(ids[q], ids[(q + 1) % 4]))
+                sv, tv = _TEXVECS[axis]
+                Pm = np.array([c[2:] for c in corners], dtype=np.float64)
+                sc_ = Pm @ np.array(sv[:3]) + sv[3]
+                tc_ = Pm @ np.array(tv[:3]) + tv[3]
+                smin, tmin = int(np.floor(sc_.min() / 16)), int(np.floor(tc_.min() / 16))
+                sw, th = int(np.ceil(sc_.max() / 16)) - smin + 1, int(np.ceil(tc_.max() / 16)) - tmin + 1
+                S, T = np.meshgrid(np.arange(sw), np.arange(th))
+                base = 90 + 25 * axis + (40 if side == 0 else 0)
+                noise = (_hash_u32(S.astype(np.int64), T.astype(np.int64), np.int64(mi * 16 + axis * 2 + side + 9000)) & 0x1F).astype(np.float64)
+                lum = np.clip(base + 6.0 * S + 4.0 * T + noise, 0, 255)
+                rgb = np.stack([lum, np.clip(lum * 0.9 + 10, 0, 255), np.clip(lum * 0.8 + (mi % 3) * 20, 0, 255)], -1).astype(np.uint8)
+                lightofs = len(light_blob)
+                light_blob += rgb.tobytes()
+                extra_planes.append((axis, float(pc)))
+                face_recs.append((len(b.planes) + len(extra_planes) - 1, side, first, 4, ti, [0, 255, 255, 255], lightofs))
+        submodels.append((tuple(-float(h) for h in half), tuple(float(h) for h in half), first_face, 6))
+
     # ---- marksurfaces / leafs
     marks = []
     leaf_recs = []
@@ -588,6 +640,7 @@ def generate(spec: MapSpec = MapSpec(), ncameras: int = 256) -> GeneratedMap:
     ent = '{\n"classname" "worldspawn"\n"message" "%s"\n}\n' % spec.name
     L[0] = ent.encode("ascii") + b"\0"
     L[1] = b"".join(struct.pack("<4fi", *[(1.0 if a == ax else 0.0) for a in range(3)], float(b.world(ax, c)), ax) for (ax, c) in b.planes)
+    L[1] += b"".join(struct.pack("<4fi", *[(1.0 if a == ax else 0.0) for a in range(3)], d, ax) for (ax, d) in extra_planes)
     nt = len(tex_blobs)
     hdr = struct.pack("<i", nt)
     o = 4 + 4 * nt
@@ -596,7 +649,7 @@ def generate(spec: MapSpec = MapSpec(), ncameras: int = 256) -> GeneratedMap:
         offs.append(o)
         o += len(blob)
     L[2] = hdr + struct.pack(f"<{nt}i", *offs) + b"".join(tex_blobs)
-    L[3] = b"".join(struct.pack("<3f", *map(float, p)) for p in verts)
+    L[3] = b"".join(struct.pack("<3f", *map(float, p[2:] if p[0] == "m" else p)) for p in verts)
     L[4] = bytes(vis_blob)
     node_blob = bytearray()
     for n in b.nodes:
@@ -618,7 +671,9 @@ def generate(spec: MapSpec = MapSpec(), ncameras: int = 256) -> GeneratedMap:
     L[13] = struct.pack(f"<{len(surfedges)}i", *surfedges)
     wmins = [b.world(a, 0) for a in range(3)]
     wmaxs = [b.world(a, g.shape[a]) for a in range(3)]
-    L[14] = struct.pack("<9f4i3i", *map(float, wmins), *map(float, wmaxs), 0.0, 0.0, 0.0, 0, 0, 0, 0, nvis, 0, len(face_recs))
+    L[14] = struct.pack("<9f4i3i", *map(float, wmins), *map(float, wmaxs), 0.0, 0.0, 0.0, 0, 0, 0, 0, nvis, 0, nworldfaces)
+    for (mn, mx, ff, nf) in submodels:
+        L[14] += struct.pack("<9f4i3i", *mn, *mx, 0.0, 0.0, 0.0, 0, 0, 0, 0, 0, ff, nf)
     assert len(verts) < 65536 and len(face_recs) < 65536 and len(marks) < 65536 and len(b.nodes) < 32768 and nleafs < 32768
     out = bytearray(struct.pack("<i", 30) + b"\0" * (8 * 15))
     for i in range(15):
@@ -633,7 +688,8 @@ def generate(spec: MapSpec = MapSpec(), ncameras: int = 256) -> GeneratedMap:
         marksurfaces=len(marks), textures=nt, lightbytes=len(light_blob), visbytes_row=(nvis + 7) // 8, vislump=len(vis_blob),
         bsp_bytes=len(out),
     )
-    return GeneratedMap(bytes(out), spec, stats, cams, g, b.org)
+    extras = {"brush_models": [{"modelindex": 2 + i, "mins": mn, "maxs": mx} for i, (mn, mx, _, _) in enumerate(submodels)]}
+    return GeneratedMap(bytes(out), spec, stats, cams, g, b.org, extras)
 
 
 def _rle(row: np.ndarray) -> bytes:
