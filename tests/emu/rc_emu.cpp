@@ -465,21 +465,23 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 					ev.push_back( rc_event_t{ rc_edge_u_at( &e, y ), e.surfs } );
 			std::sort( ev.begin(), ev.end(), []( const rc_event_t &a, const rc_event_t &b ) { return rc_event_key( a.u, a.surfs ) < rc_event_key( b.u, b.surfs ); } );
 			int32_t ovf = 0;
-			int ns = rc_generate_spans( ev.data(), (int)ev.size(), head_iu, tail_u, stk.data(), cnt.data(), ncands + 1, neg.data(), 64,
+			std::vector<unsigned long long> keys( ev.size());
+			for( size_t k = 0; k < ev.size(); k++ ) keys[k] = rc_event_key( ev[k].u, ev[k].surfs );
+			int ns = rc_generate_spans( keys.data(), (int)ev.size(), head_iu, tail_u, nullptr, stk.data(), cnt.data(), ncands + 1, neg.data(), 64,
 				spans.data(), (int)spans.size(), &ovf, E.bents.empty() ? nullptr : surfs.data(), y );
 			{
 				/* the bit-set formulation the scanline kernel uses must give the same spans */
 				std::vector<uint32_t> bits(( ncands + 32 ) / 32 + 1, 0u );
 				std::vector<rc_span_t> spans2( spans.size());
 				int32_t exc[32], ovf2 = 0;
-				std::vector<unsigned long long> keys( ev.size());
-				for( size_t k = 0; k < ev.size(); k++ ) keys[k] = rc_event_key( ev[k].u, ev[k].surfs );
 				int ns2 = rc_generate_spans_bits( keys.data(), (int)ev.size(), head_iu, tail_u, bits.data(), (int)bits.size(), exc, 16,
 					spans2.data(), (int)spans2.size(), &ovf2 );
 				bool same = ns2 == ns && ovf2 == ovf;
 				for( int k = 0; same && k < ns; k++ )
 					same = spans[k].u == spans2[k].u && spans[k].count == spans2[k].count && spans[k].surf == spans2[k].surf;
-				if( !same )
+				if( !same && !E.bents.empty())
+					E.counters[RC_CTR_BMODEL_TIES]++; /* pieces of brush entities that share a leaf key overlapped: the 1/z order decided */
+				else if( !same )
 				{
 					fprintf( stderr, "rc_emu: span replay mismatch view %d line %d (%d vs %d spans)\n", vi, y, ns, ns2 );
 					E.counters[RC_CTR_OVERFLOW_CANDS]++;

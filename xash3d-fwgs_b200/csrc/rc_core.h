@@ -1205,7 +1205,7 @@ RC_HD int rc_span_zi_in_front( const rc_surf_t *a, const rc_surf_t *b, int32_t u
 
 /* surfs / y: the view's surface records and the scanline - needed when brush entities are in the view (pieces that share
  * a leaf key are ordered by 1/z where they meet); NULL when there are none */
-RC_HD int32_t rc_generate_spans( const rc_event_t *ev, int32_t nev, int32_t head_iu, int32_t tail_u,
+RC_HD int32_t rc_generate_spans( const unsigned long long *keys, int32_t nev, int32_t head_iu, int32_t tail_u, const uint16_t *bsurf,
 	int32_t *stk, int32_t *cnt, int32_t stkcap, int32_t *neg, int32_t negcap, rc_span_t *spans, int32_t maxspans, int32_t *overflow,
 	const rc_surf_t *surfs, int32_t y )
 {
@@ -1217,11 +1217,14 @@ RC_HD int32_t rc_generate_spans( const rc_event_t *ev, int32_t nev, int32_t head
 
 	for( int32_t e = 0; e < nev; e++ )
 	{
-		int32_t u = ev[e].u;
+		/* keys: the line's events as sorted rc_event_key values; bsurf (optional): band-local -> view surface numbers */
+		const unsigned long long key = keys[e];
+		const int32_t u = (int32_t)((uint32_t)( key >> 32 ) ^ 0x80000000u );
 		if( u > tail_u )
 			break; /* sorted past edge_tail: R_GenerateSpans stops there */
 		int32_t iu = u >> 20;
-		int32_t trail = (int32_t)( ev[e].surfs & 0xFFFF ), lead = (int32_t)( ev[e].surfs >> 16 );
+		int32_t trail = (int32_t)((uint32_t)key >> 16 ), lead = (int32_t)((uint32_t)key & 0xFFFFu );
+		if( bsurf ) { trail = bsurf[trail]; lead = bsurf[lead]; }
 
 		if( trail )
 		{

@@ -97,6 +97,7 @@ struct rc_work_t
 	/* brush entities (k_bmodels) */
 	const rc_bent_t *bents; int32_t nbents; const int32_t *bfaces; int32_t nbfaces; /* bfaces: entity << 16 | face within it */
 	int32_t   *leafbase;                /* [nviews][numleafs] first reserved slot of a visited leaf, -1 = not visited */
+	int32_t   *viewbm;                  /* [nviews] k_bmodels posted a piece in the view: its scanlines check their events for pieces */
 	uint32_t  *bmvis;                   /* [nviews][nodewords + leafwords] node / leaf visframe bits of the view */
 	int32_t   *partbox;                 /* [nparts][6] bounding box of the part's transformed vertices as ordered int keys */
 	uint8_t   *itemvis;                 /* [nviews][nitems] k_item_cull: 0 = no triangle of the item can be drawn in the view */
@@ -255,6 +256,7 @@ __global__ void __launch_bounds__( 64 ) k_bmodels( rc_scene_t sc, rc_work_t w )
 	rc_bmodel_face( &sc, &bv, w.bents, w.nbents, ent, be->firstface + lf, clipflags, topnode, nodevis, leafvis, &out );
 	if( out.nsurfs )
 	{
+		w.viewbm[view] = 1;
 		atomicAdd( &w.counters[RC_CTR_BMODEL_SURFS], (unsigned long long)out.nsurfs );
 		atomicAdd( &w.counters[RC_CTR_SURFS], (unsigned long long)out.nsurfs );
 	}
@@ -669,7 +671,7 @@ struct Dev
 	rc_cmd2d_t *d_cmds2d = nullptr;
 	int32_t *d_pairs = nullptr; size_t cap_pairs = 0; int fast_maxcount = 0;
 	rc_bent_t *d_bents = nullptr; int32_t *d_bfaces = nullptr; int nbents = 0, nbfaces = 0;
-	int32_t *d_leafbase = nullptr; uint32_t *d_bmvis = nullptr; size_t cap_leafbase = 0, cap_bmvis = 0;
+	int32_t *d_leafbase = nullptr, *d_viewbm = nullptr; uint32_t *d_bmvis = nullptr; size_t cap_leafbase = 0, cap_bmvis = 0, cap_viewbm = 0;
 	int32_t *d_partbox = nullptr; size_t cap_partbox = 0; uint8_t *d_itemvis = nullptr; size_t cap_itemvis = 0;
 	int32_t *d_item_order = nullptr; rc_poly_t *d_polys = nullptr;
 	size_t cap_item_order = 0, cap_polys = 0;
@@ -900,6 +902,7 @@ rc_work_t make_slice( int k, int v0, int v1 )
 	ws.pairs = D.d_pairs ? D.d_pairs + (size_t)v0 * ( D.nfast_items > 0 ? D.nfast_items : 1 ) : nullptr;
 	ws.bents = D.d_bents; ws.nbents = D.nbents; ws.bfaces = D.d_bfaces; ws.nbfaces = D.nbfaces;
 	ws.leafbase = D.d_leafbase ? D.d_leafbase + (size_t)v0 * sc.numleafs : nullptr;
+	ws.viewbm = D.d_viewbm ? D.d_viewbm + v0 : nullptr;
 	ws.bmvis = D.d_bmvis ? D.d_bmvis + (size_t)v0 * ( ws.nodewords + ws.leafwords ) : nullptr;
 	ws.partbox = D.d_partbox; ws.itemvis = D.d_itemvis ? D.d_itemvis + (size_t)v0 * D.nitems : nullptr;
 	ws.sstatic = D.d_sstatic; ws.parts = D.d_parts; ws.bones = D.d_bones; ws.blight = D.d_blight; ws.mvpos = D.d_mvpos; ws.mlight = D.d_mlight;
@@ -926,6 +929,7 @@ int launch_slice( const rc_work_t &ws, int k, cudaStream_t st, cudaEvent_t *evs,
 	const rc_scene_t &sc = D.sc;
 	CK( cudaMemsetAsync( ws.cache_need, 0, sizeof( uint32_t ) * (( sc.numsurfaces * 4 + 31 ) / 32 + 1 ), st ));
 	CK( cudaMemsetAsync( ws.cache_nlist, 0, sizeof( int32_t ) * 16, st ));
+	if( D.nbents ) CK( cudaMemsetAsync( ws.viewbm, 0, sizeof( int32_t ) * (size_t)ws.nviews, st ));
 	if( D.nbents ) CK( cudaMemsetAsync( ws.leafbase, 0xFF, sizeof( int32_t ) * (size_t)ws.nviews * sc.numleafs, st ));
 	if( evs ) CK( cudaEventRecord( evs[0], st ));
 	k_viswalk<VW_NTHREADS><<<ws.nviews < D.vw_grid ? ws.nviews : D.vw_grid, VW_NTHREADS, (size_t)ws.vis_smem, st>>>( sc, ws );
@@ -1108,7 +1112,7 @@ void rc_dev_shutdown( void )
 	cudaDeviceSynchronize();
 	free_batch();
 	/* everything rc_dev_init / the uploads created, so that R_Shutdown + R_Init (vid_restart) starts clean */
-	void **ptrs[] = { (void **)&D.d_bents, (void **)&D.d_bfaces, (void **)&D.d_leafbase, (void **)&D.d_bmvis, (void **)&D.d_pairs, (void **)&D.d_partbox, (void **)&D.d_itemvis, (void **)&D.d_cmds2d, (void **)&D.d_trikeys, (void **)&D.d_biglist, (void **)&D.d_sstatic, (void **)&D.d_parts, (void **)&D.d_bones, (void **)&D.d_blight, (void **)&D.d_mvpos, (void **)&D.d_mlight, (void **)&D.d_item_order, (void **)&D.d_polys, (void **)&D.d_alphamap, (void **)&D.d_addmap, (void **)&D.d_modmap, (void **)&D.d_items, (void **)&D.d_corners, (void **)&D.d_sortents, (void **)&D.d_display, (void **)&D.d_screenmap, (void **)&D.d_dlights, (void **)&D.d_dlightbits,
+	void **ptrs[] = { (void **)&D.d_bents, (void **)&D.d_bfaces, (void **)&D.d_leafbase, (void **)&D.d_viewbm, (void **)&D.d_bmvis, (void **)&D.d_pairs, (void **)&D.d_partbox, (void **)&D.d_itemvis, (void **)&D.d_cmds2d, (void **)&D.d_trikeys, (void **)&D.d_biglist, (void **)&D.d_sstatic, (void **)&D.d_parts, (void **)&D.d_bones, (void **)&D.d_blight, (void **)&D.d_mvpos, (void **)&D.d_mlight, (void **)&D.d_item_order, (void **)&D.d_polys, (void **)&D.d_alphamap, (void **)&D.d_addmap, (void **)&D.d_modmap, (void **)&D.d_items, (void **)&D.d_corners, (void **)&D.d_sortents, (void **)&D.d_display, (void **)&D.d_screenmap, (void **)&D.d_dlights, (void **)&D.d_dlightbits,
 		(void **)&D.d_colormap, (void **)&D.d_lightgamma, (void **)&D.d_sintable, (void **)&D.d_textures, (void **)&D.d_texels,
 		(void **)&D.d_styles, (void **)&D.d_keys, (void **)&D.d_need, (void **)&D.d_list, (void **)&D.d_nlist,
 		(void **)&D.d_counters, &D.d_flush };
@@ -1118,7 +1122,7 @@ void rc_dev_shutdown( void )
 	D.cap_cands = D.cap_edges = D.cap_blk_events = 0; D.caps_dirty = false;
 	D.nitems = D.ncorners = D.nsortents = 0; D.h_items.clear(); D.ntris = 0; D.cap_item_order = D.cap_polys = 0;
 	D.nparts = D.totalverts = D.totalnorms = 0; D.cap_mvpos = D.cap_mlight = 0; D.studio_dirty = false;
-	D.nfast_items = D.fast_tris = 0; D.cap_trikeys = D.cap_big = 0; D.cap_partbox = D.cap_itemvis = D.cap_pairs = 0; D.nbents = D.nbfaces = 0; D.cap_leafbase = D.cap_bmvis = 0;
+	D.nfast_items = D.fast_tris = 0; D.cap_trikeys = D.cap_big = 0; D.cap_partbox = D.cap_itemvis = D.cap_pairs = 0; D.nbents = D.nbfaces = 0; D.cap_leafbase = D.cap_bmvis = D.cap_viewbm = 0;
 	D.display_bytes = 0; D.ndlights = 0; D.screen_bpp = 0; D.cache_texels = 0; D.ntextures = 0;
 	D.sc = rc_scene_t{}; D.h_surfaces.clear(); D.h_textures.clear();
 	cudaStream_t *streams[] = { &D.stream, &D.copy };
@@ -1402,6 +1406,7 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 			const size_t need_l = (size_t)D.cap_views * D.sc.numleafs, need_b = (size_t)D.cap_views * ( D.w.nodewords + D.w.leafwords );
 			if( need_l > D.cap_leafbase ) { if( dalloc( &D.d_leafbase, need_l ) != 0 ) return -1; D.cap_leafbase = need_l; }
 			if( need_b > D.cap_bmvis ) { if( dalloc( &D.d_bmvis, need_b ) != 0 ) return -1; D.cap_bmvis = need_b; }
+			if( (size_t)D.cap_views > D.cap_viewbm ) { if( dalloc( &D.d_viewbm, (size_t)D.cap_views ) != 0 ) return -1; D.cap_viewbm = D.cap_views; }
 		}
 		if( D.nitems && D.ntris )
 		{

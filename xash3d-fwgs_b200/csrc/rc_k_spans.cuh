@@ -440,6 +440,31 @@ __device__ __forceinline__ int32_t rc_replay_warp( const unsigned long long *key
 	return nspans;
 }
 
+/* brush entities: a scanline that carries a piece of one is replayed by the serial generator that keeps R_LeadingEdge's
+ * 1/z order among pieces with one leaf key (rc_generate_spans); views without brush entities never get here */
+#define SP_EXACT_STK 96
+__device__ __forceinline__ bool rc_line_has_bmodel( const rc_work_t &w, int view, const unsigned long long *keys, int32_t n, const uint16_t *bsurf, int lane, int nlanes )
+{
+	if( !w.nbents || !w.viewbm[view] )
+		return false;
+	const rc_surf_t *vs = w.surfs + (size_t)view * w.max_cands;
+	bool any = false;
+	for( int32_t i = lane; i < n; i += nlanes )
+	{
+		const uint32_t lead = (uint32_t)keys[i] & 0xFFFFu;
+		if( lead ) any = any || ( vs[bsurf[lead] - 1].emitted >> 8 ) != 0;
+	}
+	return any;
+}
+
+__device__ __noinline__ int32_t rc_replay_exact( const rc_work_t &w, int view, int32_t y, const unsigned long long *keys, int32_t n, int32_t head_iu, int32_t tail_u,
+	const uint16_t *bsurf, rc_span_t *spans, int32_t *ovf )
+{
+	int32_t stk[SP_EXACT_STK], cnt[SP_EXACT_STK], neg[2 * SP_EXCCAP];
+	return rc_generate_spans( keys, n, head_iu, tail_u, bsurf, stk, cnt, SP_EXACT_STK, neg, SP_EXCCAP, spans, n + 1, ovf,
+		w.surfs + (size_t)view * w.max_cands, y );
+}
+
 __global__ void __launch_bounds__( LN_WARPS * 32, 8 ) k_lines( rc_work_t w )
 {
 	__shared__ __align__( 16 ) unsigned long long s_keys[LN_WARPS][SP_SORTCAP];
@@ -450,7 +475,7 @@ __global__ void __launch_bounds__( LN_WARPS * 32, 8 ) k_lines( rc_work_t w )
 	int32_t cur = 0;
 	const int32_t nlines = w.nviews * w.height;
 	unsigned long long *keys = s_keys[warp];
-	int32_t nspans_total = 0, novf = 0, nserial = 0, nsorted = 0;
+	int32_t nspans_total = 0, novf = 0, nserial = 0, nsorted = 0, nties = 0;
 #ifdef RC_SPANS_DEBUG
 	const long long dbg_start = clock64();
 #endif
@@ -589,7 +614,18 @@ __global__ void __launch_bounds__( LN_WARPS * 32, 8 ) k_lines( rc_work_t w )
 
 		int32_t nsp = -1;
 		const int32_t tail_u = (( x0 + vw_w ) << 20 ) + 0xFFFFF;
-		if( sorted == keys )
+		if( sorted == keys && __ballot_sync( 0xFFFFFFFFu, rc_line_has_bmodel( w, view, keys, n, bsurf, lane, 32 )))
+		{
+			if( lane == 0 )
+			{
+				int32_t ovf = 0;
+				nsp = rc_replay_exact( w, view, line - view * w.height, keys, n, x0, tail_u, bsurf, reinterpret_cast<rc_span_t *>( slice ), &ovf );
+				novf += ovf;
+				nties++;
+			}
+			nsp = __shfl_sync( 0xFFFFFFFFu, nsp, 0 );
+		}
+		else if( sorted == keys )
 		{
 			/* invalid lanes of a partial round read keys[i >= n]: harmless (never used) */
 			if( nwords <= 2 ) nsp = rc_replay_warp<2>( keys, n, x0, tail_u, bsurf, reinterpret_cast<rc_span_t *>( slice ), lane );
@@ -642,6 +678,7 @@ __global__ void __launch_bounds__( LN_WARPS * 32, 8 ) k_lines( rc_work_t w )
 		if( novf ) atomicAdd( &w.counters[RC_CTR_OVERFLOW_EVENTS], (unsigned long long)novf );
 		if( nserial ) atomicAdd( &w.counters[RC_CTR_SERIAL_LINES], (unsigned long long)nserial );
 		if( nsorted ) atomicAdd( &w.counters[RC_CTR_SORTED_LINES], (unsigned long long)nsorted );
+		if( nties ) atomicAdd( &w.counters[RC_CTR_BMODEL_TIES], (unsigned long long)nties );
 	}
 }
 
@@ -847,7 +884,18 @@ __global__ void __launch_bounds__( WD_THREADS ) k_lines_wide( rc_work_t w )
 		if( warp == 0 )
 		{
 			int32_t nsp = -1;
-			if( sorted == s_keys && nwords <= SP_BITWORDS )
+			if( sorted == s_keys && __ballot_sync( 0xFFFFFFFFu, rc_line_has_bmodel( w, view, s_keys, n, bsurf, lane, 32 )))
+			{
+				if( lane == 0 )
+				{
+					int32_t ovf = 0;
+					nsp = rc_replay_exact( w, view, line - view * w.height, s_keys, n, x0, tail_u, bsurf, reinterpret_cast<rc_span_t *>( slice ), &ovf );
+					if( ovf ) atomicAdd( &w.counters[RC_CTR_OVERFLOW_EVENTS], 1ull );
+					atomicAdd( &w.counters[RC_CTR_BMODEL_TIES], 1ull );
+				}
+				nsp = __shfl_sync( 0xFFFFFFFFu, nsp, 0 );
+			}
+			else if( sorted == s_keys && nwords <= SP_BITWORDS )
 				nsp = rc_replay_sparse( s_keys, n, x0, tail_u, bsurf, reinterpret_cast<rc_span_t *>( slice ), s_bits, nwords, lane );
 			if( nsp < 0 )
 			{
