@@ -255,7 +255,65 @@ static void emu_keys_resolve( uint16_t *color, int16_t *zb, int width, int heigh
 	K_active = false;
 }
 
-static void emu_draw_items( const rc_view_t *vw, uint16_t *color, int16_t *zb, int width, int height )
+/* what a translucent brush entity needs of the view's world pass */
+struct emu_viewctx_t { const uint32_t *nodevis, *leafvis; const int32_t *leafbase, *leafkey; const uint16_t *candof; };
+
+/* R_DrawBrushModel: the entity's own edge frame, spans per scanline, D_AlphaSurf's drawers (k_tbrush_spans + k_tris_ordered) */
+static void emu_draw_tbrush( const rc_view_t *vw, const emu_viewctx_t &cx, int32_t ent, uint16_t *color, int16_t *zb, int width )
+{
+	const rc_scene_t *sc = &E.sc;
+	const rc_bent_t *be = &E.bents[ent];
+	rc_blendluts_t L = { E.colormap.data(), E.alphamap.data(), E.addmap.data(), E.modmap.data() };
+	std::vector<rc_surf_t> surfs( RC_TB_MAXSURFS );
+	std::vector<rc_edge_t> edges( RC_TB_MAXEDGES );
+	int32_t nedges = 0, ovf = 0;
+	const int32_t ns = rc_tbrush_pieces( sc, vw, E.bents.data(), (int32_t)E.bents.size(), ent, cx.nodevis, cx.leafvis, cx.leafbase, cx.leafkey, cx.candof,
+		surfs.data(), edges.data(), &nedges, nullptr, &ovf );
+	if( ovf ) E.counters[RC_CTR_OVERFLOW_BMODEL]++;
+	if( !ns ) return;
+	E.counters[RC_CTR_BMODEL_SURFS] += ns;
+	for( int32_t k = 0; k < ns; k++ )
+	{
+		const rc_surface_t *sf = &E.surfaces[surfs[k].surf];
+		if( !( sf->flags & ( RC_SURF_DRAWSKY | RC_SURF_DRAWTURB )) && sf->cache_ofs[0] >= 0 && block_stale( surfs[k].surf, 0 ))
+			build_block( surfs[k].surf, 0 );
+	}
+	const int32_t *turb = E.sintable.data() + vw->turb_phase;
+	const int x0 = vw->vrect[0], y0 = vw->vrect[1], vw_w = vw->vrect[2], vw_h = vw->vrect[3];
+	const int32_t head_iu = x0, tail_u = (( x0 + vw_w ) << 20 ) + 0xFFFFF;
+	for( int y = y0; y < y0 + vw_h; y++ )
+	{
+		rc_span_t spans[RC_TB_LINESPANS];
+		const int32_t nsp = rc_tbrush_line( surfs.data(), edges.data(), nedges, y, head_iu, tail_u, spans, RC_TB_LINESPANS, &ovf );
+		for( int32_t si = 0; si < nsp; si++ )
+		{
+			const rc_span_t &sp = spans[si];
+			if( !sp.surf ) continue;
+			const rc_surf_t *sf = &surfs[sp.surf - 1];
+			const int kind = rc_span_kind( sf );
+			if( kind == RC_KIND_SKY ) continue;
+			if( kind == RC_KIND_TURB && be->alpha == 0 ) continue;
+			const int nch = rc_span_nchunks( kind, sp.count ), cpx = kind == RC_KIND_TURB ? 16 : 8;
+			for( int j = 0; j < nch; j++ )
+			{
+				rc_chunk_t c;
+				rc_chunk_setup( vw, sf, vw->sky_color, sp.u, y, sp.count, j, &c );
+				const int n = std::min( cpx, sp.count - j * cpx );
+				for( int i = 0; i < n; i++ )
+				{
+					const size_t p = (size_t)y * width + c.u0 + i;
+					const int32_t ti = rc_pixel_texel( &c, i, turb );
+					const uint32_t texel = kind == RC_KIND_TURB ? E.texels[ti] : E.cache[ti];
+					const int32_t izi = (int32_t)((uint32_t)c.izi + (uint32_t)i * (uint32_t)c.izistep );
+					rc_alpha_pixel( &L, be->trans, (uint32_t)std::min( be->alpha, 7 ), kind == RC_KIND_TURB, texel, izi, &color[p], &zb[p] );
+				}
+			}
+		}
+	}
+	if( ovf ) E.counters[RC_CTR_OVERFLOW_EVENTS]++;
+}
+
+static void emu_draw_items( const rc_view_t *vw, const emu_viewctx_t &cx, uint16_t *color, int16_t *zb, int width, int height )
 {
 	if( E.items.empty() || !color || !zb )
 		return;
@@ -299,6 +357,7 @@ static void emu_draw_items( const rc_view_t *vw, uint16_t *color, int16_t *zb, i
 		if( K_active && idx >= nfast ) emu_keys_resolve( color, zb, width, height );
 		const rc_item_t *it = &E.items[idx];
 		if( it->tex_ofs < 0 ) continue;
+		if( it->kind == RC_ITEM_BRUSH ) { emu_draw_tbrush( vw, cx, it->first, color, zb, width ); continue; }
 		rc_fv_t poly[8];
 		if( it->kind == RC_ITEM_SPRITE )
 		{
@@ -371,10 +430,10 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 		int32_t maxc = sc->numsurfaces;
 		for( const rc_bent_t &b : E.bents ) maxc += b.numfaces * 64;
 		std::vector<rc_cand_t> cands( maxc + 1 );
-		std::vector<int32_t> leafbase( sc->numleafs + 1, -1 );
+		std::vector<int32_t> leafbase( sc->numleafs + 1, -1 ), leafkey( sc->numleafs + 1, -1 );
 		int32_t overflow = 0;
 		int ncands = rc_walk_world( sc, vw, nodevis.data(), leafmark.data(), surfmark.data(), stack.data(), stack_ints, cands.data(), maxc, &overflow,
-			E.bents.data(), (int32_t)E.bents.size(), leafbase.data());
+			E.bents.data(), (int32_t)E.bents.size(), leafbase.data(), leafkey.data());
 		if( overflow ) E.counters[RC_CTR_OVERFLOW_STACK]++;
 		E.counters[RC_CTR_CANDS] += ncands;
 		/* A3 + A5 */
@@ -423,11 +482,12 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 			rc_bmout_t out;
 			out.surfs = surfs.data(); out.max_cands = ncands;
 			out.edges = bedges.data(); out.max_edges = (int32_t)bedges.size(); out.nedges = &nbe;
-			out.leafbase = leafbase.data(); out.candof = candof.data(); out.cache_need = nullptr;
+			out.leafbase = leafbase.data(); out.candof = candof.data(); out.cache_need = nullptr; out.leafkey = nullptr;
 			out.nsurfs = 0; out.overflow = 0; out.noutmax = 0;
 			for( size_t e = 0; e < E.bents.size(); e++ )
 			{
 				const rc_bent_t *be = &E.bents[e];
+				if( be->trans ) continue; /* drawn in its turn among the sorted entities (emu_draw_tbrush) */
 				const int32_t clipflags = rc_bmodel_check_bbox( vw, be->minmaxs );
 				if( clipflags < 0 ) continue;
 				const int32_t topnode = rc_find_topnode( sc, nodevis.data(), leafmark.data(), be->minmaxs );
@@ -529,7 +589,10 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 				}
 			}
 		}
-		emu_draw_items( vw, color, zb, width, height );
+		{
+			emu_viewctx_t cx = { nodevis.data(), leafmark.data(), leafbase.data(), leafkey.data(), candof.data() };
+			emu_draw_items( vw, cx, color, zb, width, height );
+		}
 		E.vsurfs[vi] = surfs; E.vedges[vi] = edges;
 		E.counters[RC_CTR_VIEWS]++; E.counters[RC_CTR_PIXELS] += (uint64_t)vw_w * vw_h;
 	}

@@ -209,9 +209,9 @@ RC_HD int32_t rc_leaf_bmodel_slots( const rc_leaf_t *lf, const rc_bent_t *bents,
  * place in the order (= its key, LEAF_KEY r_bsp.c:541); leafbase[leaf] = the first of them (the caller presets -1) */
 RC_HD int32_t rc_walk_world( const rc_scene_t *sc, const rc_view_t *vw, const uint32_t *nodevis, const uint32_t *leafmark,
 	uint32_t *surfmark, int32_t *stack, int32_t stack_ints, rc_cand_t *cands, int32_t max_cands, int32_t *overflow,
-	const rc_bent_t *bents, int32_t nbents, int32_t *leafbase )
+	const rc_bent_t *bents, int32_t nbents, int32_t *leafbase, int32_t *leafkey )
 {
-	int32_t ncands = 0, sp = 0;
+	int32_t ncands = 0, sp = 0, nvisited = 0;
 	stack[sp++] = sc->headnode; stack[sp++] = 15;
 
 	while( sp )
@@ -269,6 +269,7 @@ RC_HD int32_t rc_walk_world( const rc_scene_t *sc, const rc_view_t *vw, const ui
 			{
 				const int32_t n = rc_leaf_bmodel_slots( leaf, bents, nbents, nbents );
 				leafbase[li] = ncands;
+				if( leafkey ) leafkey[li] = nvisited++; /* the leaf's place in the walk: a key of its own even when it reserves nothing */
 				for( int32_t k = 0; k < n; k++ )
 				{
 					if( ncands < max_cands ) { cands[ncands].surf = -1; cands[ncands].clipflags = 0; ncands++; }
@@ -787,7 +788,8 @@ RC_HD void rc_face_finish( const rc_scene_t *sc, const rc_view_t *vw, const rc_c
 		return;
 	}
 
-	int32_t miplevel = rc_miplevel_for_scale( vw, fs->nearzi * vw->scale_for_mip );
+	/* D_AlphaSurf (r_edge.c:931) always draws from mip 0; D_SolidSurf picks the level from the nearest 1/z */
+	int32_t miplevel = ( cand->clipflags & 0x100 ) ? 0 : rc_miplevel_for_scale( vw, fs->nearzi * vw->scale_for_mip );
 	while(( 1 << miplevel ) > sf->sample_size )
 		miplevel--;
 	o->miplevel = miplevel;
@@ -933,7 +935,7 @@ RC_HD int32_t rc_leaf_bmodel_slots( const rc_leaf_t *lf, const rc_bent_t *bents,
 {
 	int32_t n = 0;
 	for( int32_t e = 0; e < nbents && e < upto; e++ )
-		if( rc_bent_touches_leaf( &bents[e], lf ))
+		if( !bents[e].trans && rc_bent_touches_leaf( &bents[e], lf ))
 			n += bents[e].numfaces;
 	return n;
 }
@@ -947,6 +949,9 @@ typedef struct
 	rc_edge_t *edges; int32_t max_edges; int32_t *nedges;
 	const int32_t *leafbase;  /* [numleafs] first reserved slot of every visited leaf, -1 = not visited */
 	const uint16_t *candof;
+	const int32_t *leafkey;   /* NULL: the pieces go into the leaf's reserved slots of the view's surface list (opaque entities).
+	                           * else [numleafs] place of every visited leaf in the walk: the entity keeps a surface list of its
+	                           * own (R_DrawBrushModel's edge frame), pieces in arrival order, keyed by leafkey + 1, mip 0 */
 	uint32_t *cache_need;     /* (face, mip) blocks the batch samples (device); NULL: the caller derives them from the surfaces */
 	int32_t nsurfs, overflow, noutmax;
 } rc_bmout_t;
@@ -1002,7 +1007,7 @@ RC_HD void rc_bmodel_face( const rc_scene_t *sc, const rc_view_t *bv, const rc_b
 	rc_edge_t ebuf[RC_BM_FRAGEDGES];
 	rc_facestate_t fs;
 	rc_cand_t cand;
-	cand.surf = face; cand.clipflags = clipflags;
+	cand.surf = face; cand.clipflags = clipflags | ( out->leafkey ? 0x100 : 0 ); /* 0x100: D_AlphaSurf draws from mip 0 */
 
 	if( topnode < 0 )
 	{
@@ -1012,12 +1017,12 @@ RC_HD void rc_bmodel_face( const rc_scene_t *sc, const rc_view_t *bv, const rc_b
 		const int32_t base = out->leafbase[leaf];
 		if( base < 0 )
 			return; /* the walk never reached the leaf (outside the frustum): nothing of it can be on screen */
-		const int32_t slot = base + rc_leaf_bmodel_slots( &sc->leafs[leaf], bents, nbents, ent ) + ( face - be->firstface );
+		const int32_t slot = out->leafkey ? out->nsurfs : base + rc_leaf_bmodel_slots( &sc->leafs[leaf], bents, nbents, ent ) + ( face - be->firstface );
 		if( slot >= out->max_cands ) { out->overflow = 1; return; }
 		int mkl, mkr;
 		rc_bm_fs_init( &fs, ebuf, slot );
 		rc_face_edges( sc, bv, &cand, out->candof, 0, &fs, &mkl, &mkr );
-		rc_bmodel_post( sc, bv, &cand, &fs, mkl, mkr, slot, base + 1, out );
+		rc_bmodel_post( sc, bv, &cand, &fs, mkl, mkr, slot, out->leafkey ? out->leafkey[leaf] + 1 : base + 1, out );
 		return;
 	}
 
@@ -1063,7 +1068,7 @@ RC_HD void rc_bmodel_face( const rc_scene_t *sc, const rc_view_t *bv, const rc_b
 			const int32_t base = out->leafbase[leaf];
 			if( base < 0 )
 				continue;
-			const int32_t slot = base + rc_leaf_bmodel_slots( &sc->leafs[leaf], bents, nbents, ent ) + ( face - be->firstface );
+			const int32_t slot = out->leafkey ? out->nsurfs : base + rc_leaf_bmodel_slots( &sc->leafs[leaf], bents, nbents, ent ) + ( face - be->firstface );
 			if( slot >= out->max_cands ) { out->overflow = 1; continue; }
 			/* R_RenderBmodelFace */
 			int mkl = 0, mkr = 0;
@@ -1075,7 +1080,7 @@ RC_HD void rc_bmodel_face( const rc_scene_t *sc, const rc_view_t *bv, const rc_b
 				if( fs.leftclipped ) mkl = 1;
 				if( fs.rightclipped ) mkr = 1;
 			}
-			rc_bmodel_post( sc, bv, &cand, &fs, mkl, mkr, slot, base + 1, out );
+			rc_bmodel_post( sc, bv, &cand, &fs, mkl, mkr, slot, out->leafkey ? out->leafkey[leaf] + 1 : base + 1, out );
 			continue;
 		}
 		if( !rc_testbit( nodevis, node ))
@@ -1431,6 +1436,61 @@ RC_HD int32_t rc_generate_spans_bits( const unsigned long long *keys, int32_t ne
 	}
 #undef RC_EMIT_SPAN
 	return nspans;
+}
+
+/* ------------------------------------------------------------------------------------------ */
+/* A12: translucent brush entities - R_DrawBrushModel (ref/soft/r_main.c:861): an edge frame of the entity's own   */
+/* (R_BeginEdgeFrame .. R_ScanEdges with alphaspans), its pieces keyed by the leaves the world pass numbered        */
+
+/* the entity's pieces in one view: surface records (mip 0, leaf keys) and edges; returns the piece count */
+RC_HD int32_t rc_tbrush_pieces( const rc_scene_t *sc, const rc_view_t *vw, const rc_bent_t *bents, int32_t nbents, int32_t ent,
+	const uint32_t *nodevis, const uint32_t *leafvis, const int32_t *leafbase, const int32_t *leafkey, const uint16_t *candof,
+	rc_surf_t *surfs, rc_edge_t *edges, int32_t *nedges, uint32_t *cache_need, int32_t *overflow )
+{
+	const rc_bent_t *be = &bents[ent];
+	*nedges = 0;
+	const int32_t clipflags = rc_bmodel_check_bbox( vw, be->minmaxs );
+	if( clipflags < 0 )
+		return 0;
+	const int32_t topnode = rc_find_topnode( sc, nodevis, leafvis, be->minmaxs );
+	if( topnode == RC_TOPNODE_NONE )
+		return 0;
+	rc_view_t bv;
+	rc_bmodel_view( vw, be, &bv );
+	rc_bmout_t out;
+	out.surfs = surfs; out.max_cands = RC_TB_MAXSURFS;
+	out.edges = edges; out.max_edges = RC_TB_MAXEDGES; out.nedges = nedges;
+	out.leafbase = leafbase; out.leafkey = leafkey; out.candof = candof; out.cache_need = cache_need;
+	out.nsurfs = 0; out.overflow = 0; out.noutmax = 0;
+	for( int32_t f = 0; f < be->numfaces; f++ )
+		rc_bmodel_face( sc, &bv, bents, nbents, ent, be->firstface + f, clipflags, topnode, nodevis, leafvis, &out );
+	if( out.overflow || out.noutmax > RC_TB_MAXEDGES ) *overflow = 1;
+	if( *nedges > RC_TB_MAXEDGES ) *nedges = RC_TB_MAXEDGES;
+	return out.nsurfs;
+}
+
+/* R_ScanEdges for one scanline of that edge frame: the events of the line, sorted, through the span generator */
+#define RC_TB_LINEEVENTS 64
+RC_HD int32_t rc_tbrush_line( const rc_surf_t *surfs, const rc_edge_t *edges, int32_t nedges, int32_t y, int32_t head_iu, int32_t tail_u,
+	rc_span_t *spans, int32_t maxspans, int32_t *overflow )
+{
+	unsigned long long keys[RC_TB_LINEEVENTS];
+	int32_t n = 0;
+	for( int32_t i = 0; i < nedges; i++ )
+	{
+		if( !rc_edge_active( &edges[i], y ))
+			continue;
+		if( n >= RC_TB_LINEEVENTS ) { *overflow = 1; break; }
+		const unsigned long long key = rc_event_key( rc_edge_u_at( &edges[i], y ), edges[i].surfs );
+		int32_t j = n - 1;
+		while( j >= 0 && keys[j] > key ) { keys[j + 1] = keys[j]; j--; }
+		keys[j + 1] = key;
+		n++;
+	}
+	if( !n )
+		return 0;
+	int32_t stk[RC_TB_MAXSURFS], cnt[RC_TB_MAXSURFS], neg[16];
+	return rc_generate_spans( keys, n, head_iu, tail_u, (const uint16_t *)0, stk, cnt, RC_TB_MAXSURFS, neg, 8, spans, maxspans, overflow, surfs, y );
 }
 
 /* ------------------------------------------------------------------------------------------ */

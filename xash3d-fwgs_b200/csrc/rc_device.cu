@@ -251,7 +251,7 @@ __global__ void __launch_bounds__( 64 ) k_bmodels( rc_scene_t sc, rc_work_t w )
 	out.edges = w.edges + (size_t)view * w.max_edges; out.max_edges = w.max_edges; out.nedges = &w.nedges[view];
 	out.leafbase = w.leafbase + (size_t)view * sc.numleafs;
 	out.candof = w.candof + (size_t)view * ( sc.numsurfaces + 2 );
-	out.cache_need = w.cache_need;
+	out.cache_need = w.cache_need; out.leafkey = nullptr;
 	out.nsurfs = 0; out.overflow = 0; out.noutmax = 0;
 	rc_bmodel_face( &sc, &bv, w.bents, w.nbents, ent, be->firstface + lf, clipflags, topnode, nodevis, leafvis, &out );
 	if( out.nsurfs )
@@ -1291,7 +1291,7 @@ int rc_dev_set_bents( const rc_bent_t *bents, int n )
 	if( n <= 0 ) return 0;
 	std::vector<int32_t> bf;
 	for( int e = 0; e < n; e++ )
-		for( int f = 0; f < bents[e].numfaces && f < 65536; f++ ) bf.push_back(( e << 16 ) | f );
+		for( int f = 0; !bents[e].trans && f < bents[e].numfaces && f < 65536; f++ ) bf.push_back(( e << 16 ) | f );
 	if( upload( &D.d_bents, bents, (size_t)n ) != 0 ) return -1;
 	if( upload( &D.d_bfaces, bf.data(), bf.size()) != 0 ) return -1;
 	D.h2d_bytes += sizeof( rc_bent_t ) * (size_t)n + 4 * bf.size();

@@ -1254,6 +1254,8 @@ static void rc_add_studio( cl_entity_t *e );
 
 /* R_DrawEntitiesOnList (ref/soft/r_main.c:504-635) as a list of draw items: solid studio models, solid sprites, the
  * client's opaque triangles, then the translucent entities (each with a sort record) and the client's translucent ones */
+static void rc_add_tbrush( cl_entity_t *e );
+
 static void rc_build_items( void )
 {
 	rc.nitems = rc.ncorners = rc.nsortents = 0;
@@ -1300,9 +1302,7 @@ static void rc_build_items( void )
 		{
 		case mod_studio: rc_add_studio( e ); break;
 		case mod_sprite: rc_add_sprite( e ); break;
-		case mod_brush:
-			if( !rc.warned[3] ) { rc.warned[3] = true; gEngfuncs.Con_Reportf( "ref_cuda: translucent brush entities are not drawn yet\n" ); }
-			break;
+		case mod_brush: rc_add_tbrush( e ); break;
 		default: break;
 		}
 		rc.sortents[rc.cur_sortent].nitems = rc.nitems - rc.sortents[rc.cur_sortent].first_item;
@@ -1319,6 +1319,7 @@ static void rc_build_items( void )
 	{
 		rc_item_t *it = &rc.items[i];
 		const rc_image_t *img = &rc.images[it->tex_ofs];
+		if( it->kind == RC_ITEM_BRUSH ) { it->tex_ofs = 0; it->order0 = order; continue; }
 		const rc_texture_t *t = rc_texture_entry( it->tex_ofs );
 		it->tex_ofs = t ? ( it->drawer == RC_DRAW_TEXBLEND ? t->alpha_ofs : t->ofs[0] ) : -1;
 		(void)img;
@@ -1918,60 +1919,85 @@ static void rc_concat_rotations( float in1[3][3], float in2[3][3], float out[3][
 			out[i][j] = in1[i][0] * in2[0][j] + in1[i][1] * in2[1][j] + in1[i][2] * in2[2][j];
 }
 
-static void rc_build_bents( void )
+static rc_bent_t rc_bents[RC_MAX_BENTS];
+static int rc_nbents;
+
+/* -> index of the new record, -1 = not a drawable brush model / table full */
+static int rc_make_bent( cl_entity_t *e )
 {
-	static rc_bent_t bents[RC_MAX_BENTS];
-	int n = 0;
-	for( int i = 0; i < rc.num_edge && n < RC_MAX_BENTS; i++ )
+	model_t *mod = e->model;
+	if( !mod || mod->nummodelsurfaces == 0 || mod->type != mod_brush || rc_nbents >= RC_MAX_BENTS )
+		return -1;
+	rc_bent_t *b = &rc_bents[rc_nbents];
+	memset( b, 0, sizeof( *b ));
+	/* RotatedBBox */
+	vec3_t tmins, tmaxs;
+	if( !e->angles[0] && !e->angles[1] && !e->angles[2] )
 	{
-		cl_entity_t *e = rc.edge_ents[i];
-		model_t *mod = e->model;
-		if( !mod || mod->nummodelsurfaces == 0 || mod->type != mod_brush )
-			continue;
-		rc_bent_t *b = &bents[n++];
-		memset( b, 0, sizeof( *b ));
-		/* RotatedBBox */
-		vec3_t tmins, tmaxs;
-		if( !e->angles[0] && !e->angles[1] && !e->angles[2] )
+		VectorCopy( mod->mins, tmins ); VectorCopy( mod->maxs, tmaxs );
+	}
+	else
+	{
+		vec3_t forward, right, up, tmp, v;
+		for( int k = 0; k < 3; k++ ) { tmins[k] = 99999; tmaxs[k] = -99999; }
+		AngleVectors( e->angles, forward, right, up );
+		for( int c = 0; c < 8; c++ )
 		{
-			VectorCopy( mod->mins, tmins ); VectorCopy( mod->maxs, tmaxs );
-		}
-		else
-		{
-			vec3_t forward, right, up, tmp, v;
-			for( int k = 0; k < 3; k++ ) { tmins[k] = 99999; tmaxs[k] = -99999; }
-			AngleVectors( e->angles, forward, right, up );
-			for( int c = 0; c < 8; c++ )
+			tmp[0] = ( c & 1 ) ? mod->mins[0] : mod->maxs[0];
+			tmp[1] = ( c & 2 ) ? mod->mins[1] : mod->maxs[1];
+			tmp[2] = ( c & 4 ) ? mod->mins[2] : mod->maxs[2];
+			VectorScale( forward, tmp[0], v );
+			VectorMA( v, -tmp[1], right, v );
+			VectorMA( v, tmp[2], up, v );
+			for( int j = 0; j < 3; j++ )
 			{
-				tmp[0] = ( c & 1 ) ? mod->mins[0] : mod->maxs[0];
-				tmp[1] = ( c & 2 ) ? mod->mins[1] : mod->maxs[1];
-				tmp[2] = ( c & 4 ) ? mod->mins[2] : mod->maxs[2];
-				VectorScale( forward, tmp[0], v );
-				VectorMA( v, -tmp[1], right, v );
-				VectorMA( v, tmp[2], up, v );
-				for( int j = 0; j < 3; j++ )
-				{
-					if( v[j] < tmins[j] ) tmins[j] = v[j];
-					if( v[j] > tmaxs[j] ) tmaxs[j] = v[j];
-				}
+				if( v[j] < tmins[j] ) tmins[j] = v[j];
+				if( v[j] > tmaxs[j] ) tmaxs[j] = v[j];
 			}
 		}
-		VectorAdd( tmins, e->origin, b->minmaxs );
-		VectorAdd( tmaxs, e->origin, ( b->minmaxs + 3 ));
-		VectorCopy( e->origin, b->origin );
-		/* R_RotateBmodel: yaw, pitch, roll */
-		float angle, sn, cs, temp1[3][3], temp2[3][3], temp3[3][3];
-		angle = e->angles[YAW]; angle = angle * M_PI_F * 2 / 360.0f; sn = sin( angle ); cs = cos( angle );
-		temp1[0][0] = cs; temp1[0][1] = sn; temp1[0][2] = 0; temp1[1][0] = -sn; temp1[1][1] = cs; temp1[1][2] = 0; temp1[2][0] = 0; temp1[2][1] = 0; temp1[2][2] = 1;
-		angle = e->angles[PITCH]; angle = angle * M_PI_F * 2 / 360.0f; sn = sin( angle ); cs = cos( angle );
-		temp2[0][0] = cs; temp2[0][1] = 0; temp2[0][2] = -sn; temp2[1][0] = 0; temp2[1][1] = 1; temp2[1][2] = 0; temp2[2][0] = sn; temp2[2][1] = 0; temp2[2][2] = cs;
-		rc_concat_rotations( temp2, temp1, temp3 );
-		angle = e->angles[ROLL]; angle = angle * M_PI_F * 2 / 360.0f; sn = sin( angle ); cs = cos( angle );
-		temp1[0][0] = 1; temp1[0][1] = 0; temp1[0][2] = 0; temp1[1][0] = 0; temp1[1][1] = cs; temp1[1][2] = sn; temp1[2][0] = 0; temp1[2][1] = -sn; temp1[2][2] = cs;
-		rc_concat_rotations( temp1, temp3, b->rot );
-		b->firstface = mod->firstmodelsurface; b->numfaces = mod->nummodelsurfaces;
 	}
-	RC_CHECK_DEV( rc_dev_set_bents( bents, n ));
+	VectorAdd( tmins, e->origin, b->minmaxs );
+	VectorAdd( tmaxs, e->origin, ( b->minmaxs + 3 ));
+	VectorCopy( e->origin, b->origin );
+	/* R_RotateBmodel: yaw, pitch, roll */
+	float angle, sn, cs, temp1[3][3], temp2[3][3], temp3[3][3];
+	angle = e->angles[YAW]; angle = angle * M_PI_F * 2 / 360.0f; sn = sin( angle ); cs = cos( angle );
+	temp1[0][0] = cs; temp1[0][1] = sn; temp1[0][2] = 0; temp1[1][0] = -sn; temp1[1][1] = cs; temp1[1][2] = 0; temp1[2][0] = 0; temp1[2][1] = 0; temp1[2][2] = 1;
+	angle = e->angles[PITCH]; angle = angle * M_PI_F * 2 / 360.0f; sn = sin( angle ); cs = cos( angle );
+	temp2[0][0] = cs; temp2[0][1] = 0; temp2[0][2] = -sn; temp2[1][0] = 0; temp2[1][1] = 1; temp2[1][2] = 0; temp2[2][0] = sn; temp2[2][1] = 0; temp2[2][2] = cs;
+	rc_concat_rotations( temp2, temp1, temp3 );
+	angle = e->angles[ROLL]; angle = angle * M_PI_F * 2 / 360.0f; sn = sin( angle ); cs = cos( angle );
+	temp1[0][0] = 1; temp1[0][1] = 0; temp1[0][2] = 0; temp1[1][0] = 0; temp1[1][1] = cs; temp1[1][2] = sn; temp1[2][0] = 0; temp1[2][1] = -sn; temp1[2][2] = cs;
+	rc_concat_rotations( temp1, temp3, b->rot );
+	b->firstface = mod->firstmodelsurface; b->numfaces = mod->nummodelsurfaces;
+	return rc_nbents++;
+}
+
+/* the frame's edge_entities (opaque); the translucent ones join the table as rc_build_items reaches them */
+static void rc_build_bents( void )
+{
+	rc_nbents = 0;
+	for( int i = 0; i < rc.num_edge; i++ )
+		rc_make_bent( rc.edge_ents[i] );
+}
+
+/* R_DrawBrushModel (r_main.c:861) for a translucent entity: a draw item in the sorted sequence; the span drawer and the
+ * alpha are D_AlphaSurf's (r_edge.c:931-960) */
+static void rc_add_tbrush( cl_entity_t *e )
+{
+	const int bi = rc_make_bent( e );
+	if( bi < 0 )
+		return;
+	rc_bent_t *b = &rc_bents[bi];
+	int alpha = e->curstate.renderamt * 7 / 255;
+	if( alpha <= 0 && e->curstate.renderamt > 0 )
+		alpha = 1;
+	b->alpha = alpha;
+	b->trans = e->curstate.rendermode == kRenderTransAlpha ? RC_TB_ALPHATEST : e->curstate.rendermode == kRenderTransAdd ? RC_TB_ADD : RC_TB_BLEND;
+	rc_item_t *it = rc_new_item( RC_ITEM_BRUSH );
+	it->first = bi; it->count = 0;
+	it->tex_ofs = 0; /* no skin: the pieces sample the surface cache */
+	it->alpha = alpha;
 }
 
 /* LightToTexGamma (ref/soft/r_local.h:518-523) reads the engine's live table, or nothing in linear gamma space */
@@ -2009,6 +2035,7 @@ static void rc_prepare_batch( void )
 	rc_push_dlights();
 	rc_build_bents();
 	rc_build_items();
+	RC_CHECK_DEV( rc_dev_set_bents( rc_bents, rc_nbents ));
 }
 
 static void rc_queue_view( const ref_viewpass_t *rvp )

@@ -159,7 +159,7 @@ typedef struct
  * turns the frame's entity lists into an ordered list of draw items - the order R_DrawEntitiesOnList (r_main.c:504)
  * draws in; translucent entities come with a sort record, their order is per view (R_TransEntityCompare, r_main.c:157).
  */
-enum { RC_ITEM_TRIS = 0, RC_ITEM_SPRITE = 1, RC_ITEM_MESH = 2 };
+enum { RC_ITEM_TRIS = 0, RC_ITEM_SPRITE = 1, RC_ITEM_MESH = 2, RC_ITEM_BRUSH = 3 /* a translucent brush entity: first = its rc_bent_t */ };
 /* the span drawer a texture bind selects (GL_Bind, ref/soft/r_image.c:43-75): R_PolysetFillSpans8, ...Additive, ...Glow,
  * ...TextureBlended, ...Blended (r_polyse.c:724-1214) */
 enum { RC_DRAW_FILL = 0, RC_DRAW_ADDITIVE = 1, RC_DRAW_GLOW = 2, RC_DRAW_TEXBLEND = 3, RC_DRAW_BLEND = 4 };
@@ -236,8 +236,14 @@ typedef struct
 	float   rot[3][3];       /* entity_rotation (R_RotateBmodel, r_bsp.c:97): yaw, pitch, roll matrices concatenated on the host */
 	float   minmaxs[6];      /* RotatedBBox + origin */
 	int32_t firstface, numfaces;
-	int32_t pad[2];
-} rc_bent_t; /* 92 B -> 96 */
+	int32_t trans;           /* 0: opaque (edge_entities).  RC_TB_*: a translucent entity, drawn in its turn among the sorted
+	                          * entities by R_DrawBrushModel (r_main.c:861) through D_AlphaSurf's span drawers (r_edge.c:904) */
+	int32_t alpha;           /* D_AlphaSurf: renderamt * 7 / 255, at least 1 */
+} rc_bent_t; /* 96 B */
+enum { RC_TB_ALPHATEST = 1 /* kRenderTransAlpha: D_AlphaSpans16 */, RC_TB_ADD = 2 /* kRenderTransAdd: D_AddSpans16 */, RC_TB_BLEND = 3 /* D_BlendSpans16 */ };
+#define RC_TB_MAXSURFS 64   /* pieces one translucent brush entity can have in a view */
+#define RC_TB_MAXEDGES 384
+#define RC_TB_LINESPANS 24  /* spans of one entity on one scanline */
 
 /* a 2-D draw of the frame's HUD pass (R_DrawStretchPic / Draw_Fill, ref/soft/r_draw.c:38,159), clipped on the host */
 enum { RC_2D_PIC = 0, RC_2D_FILL = 1 };

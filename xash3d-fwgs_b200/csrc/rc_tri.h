@@ -500,6 +500,27 @@ RC_HD void rc_tri_shade( const rc_blendluts_t *L, int drawer, uint32_t color, ui
 }
 
 /* ------------------------------------------------------------------------------------------ */
+/* translucent brush entities: one pixel of D_AlphaSpans16 / D_BlendSpans16 / D_AddSpans16 / D_DrawTurbulent8ZSpan
+ * (ref/soft/r_scan.c:698,898,1109,59): texel = what the span's s, t select in the cache block (the texture, for water),
+ * izi the span's 1/z accumulator at the pixel */
+RC_HD void rc_alpha_pixel( const rc_blendluts_t *L, int mode, uint32_t alpha, int turb, uint32_t texel, int32_t izi, uint16_t *pc, int16_t *pz )
+{
+	const int32_t z16 = izi >> 16;
+	if( !( (int32_t)*pz <= z16 ))
+		return;
+	if( turb )
+	{
+		*pc = (uint16_t)( alpha == 7 ? texel : rc_blend_alpha( L, alpha, texel, *pc ));
+		return;
+	}
+	if( texel == 0x0349u ) /* TRANSPARENT_COLOR */
+		return;
+	if( mode == RC_TB_ALPHATEST ) { *pc = (uint16_t)texel; *pz = (int16_t)z16; }
+	else if( mode == RC_TB_ADD ) *pc = (uint16_t)rc_blend_add( L, texel, *pc );
+	else *pc = (uint16_t)( alpha != 7 ? rc_blend_alpha( L, alpha, texel, *pc ) : texel );
+}
+
+/* ------------------------------------------------------------------------------------------ */
 /* the HUD pass: one destination pixel of R_DrawStretchPicImplementation / Draw_Fill (ref/soft/r_draw.c:88-135,192-210) */
 RC_HD void rc_2d_pixel( const rc_blendluts_t *L, const rc_cmd2d_t *c, const uint16_t *texels, int32_t v, uint32_t u, uint16_t *dest )
 {
