@@ -178,3 +178,22 @@ def test_scalar_brush_entity_path_matches_oracle(pkg, scene, rotate):
     assert np.array_equal(a, rc) and np.array_equal(az, rz)
     ctr = emu.counters()
     assert ctr["bmodel_surfs"] > 100 and ctr["overflow_bmodel"] == 0
+
+
+def test_scalar_translucent_brush_entities_match_oracle(pkg, scene):
+    """SURVEY 8a A12 through the CPU debug harness: R_DrawBrushModel in the sorted entity sequence - an edge frame per entity
+    (rc_tbrush_pieces / rc_tbrush_line), D_BlendSpans16 / D_AddSpans16 / D_AlphaSpans16 pixels (rc_alpha_pixel) - next to
+    opaque brush entities."""
+    m = scene.make_map("small", ncameras=64, brush_models=6)
+    emu = scene.Renderer(EMU_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    opaque_only = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    scene.add_brush_entities(opaque_only, m, m.cameras, 8, rotate=True)
+    base, _ = opaque_only.render_views(m.cameras[:28])
+    for r in (emu, so):
+        scene.add_mixed_brush_entities(r, m, m.cameras)
+    a, az = emu.render_views(m.cameras[:28])
+    rc, rz = so.render_views(m.cameras[:28])
+    assert (rc != base).mean() > 0.05, "the oracle drew no translucent brush entities"
+    assert np.array_equal(a, rc) and np.array_equal(az, rz)
+    assert emu.counters()["overflow_bmodel"] == 0

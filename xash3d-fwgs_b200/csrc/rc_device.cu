@@ -97,6 +97,10 @@ struct rc_work_t
 	/* brush entities (k_bmodels) */
 	const rc_bent_t *bents; int32_t nbents; const int32_t *bfaces; int32_t nbfaces; /* bfaces: entity << 16 | face within it */
 	int32_t   *leafbase;                /* [nviews][numleafs] first reserved slot of a visited leaf, -1 = not visited */
+	int32_t   *leafkey;                 /* [nviews][numleafs] place of a visited leaf in the walk (translucent brush entities) */
+	/* translucent brush entities (k_tbrush_pieces -> k_tris_ordered): per (view, entity) an edge frame of its own */
+	const int32_t *tbord; int32_t ntb;  /* bent index -> ordinal among the translucent ones (-1: opaque) */
+	rc_surf_t *tb_surfs; rc_edge_t *tb_edges; int32_t *tb_counts; /* [nviews][ntb][RC_TB_MAXSURFS | RC_TB_MAXEDGES | 2 = pieces, edges] */
 	int32_t   *viewbm;                  /* [nviews] k_bmodels posted a piece in the view: its scanlines check their events for pieces */
 	uint32_t  *bmvis;                   /* [nviews][nodewords + leafwords] node / leaf visframe bits of the view */
 	int32_t   *partbox;                 /* [nparts][6] bounding box of the part's transformed vertices as ordered int keys */
@@ -262,6 +266,30 @@ __global__ void __launch_bounds__( 64 ) k_bmodels( rc_scene_t sc, rc_work_t w )
 	}
 	if( out.overflow ) atomicAdd( &w.counters[RC_CTR_OVERFLOW_BMODEL], 1ull );
 	if( out.noutmax > w.max_edges ) atomicAdd( &w.counters[RC_CTR_OVERFLOW_EDGES], 1ull );
+}
+
+/* translucent brush entities (rc_core.h A12): thread per (view, entity) - the pieces of R_DrawBrushModel's own edge frame,
+ * kept per (view, entity) for k_tris_ordered, which draws them in the entity's turn; the mip-0 cache blocks they sample
+ * join the batch's build list (this runs before k_cache_list) */
+__global__ void __launch_bounds__( 64 ) k_tbrush_pieces( rc_scene_t sc, rc_work_t w )
+{
+	const int32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+	if( g >= w.nviews * w.nbents )
+		return;
+	const int view = g / w.nbents, ent = g - view * w.nbents;
+	const int32_t tb = w.tbord[ent];
+	if( tb < 0 )
+		return;
+	const size_t slot = (size_t)view * w.ntb + tb;
+	const uint32_t *nodevis = w.bmvis + (size_t)view * ( w.nodewords + w.leafwords ), *leafvis = nodevis + w.nodewords;
+	int32_t ovf = 0;
+	int32_t *pnedges = &w.tb_counts[2 * slot + 1]; /* the edge cursor is advanced with an atomic: it has to live in global memory */
+	const int32_t ns = rc_tbrush_pieces( &sc, &w.views[view], w.bents, w.nbents, ent, nodevis, leafvis, w.leafbase + (size_t)view * sc.numleafs,
+		w.leafkey + (size_t)view * sc.numleafs, w.candof + (size_t)view * ( sc.numsurfaces + 2 ),
+		w.tb_surfs + slot * RC_TB_MAXSURFS, w.tb_edges + slot * RC_TB_MAXEDGES, pnedges, w.cache_need, &ovf );
+	w.tb_counts[2 * slot] = ns;
+	if( ns ) atomicAdd( &w.counters[RC_CTR_BMODEL_SURFS], (unsigned long long)ns );
+	if( ovf ) atomicAdd( &w.counters[RC_CTR_OVERFLOW_BMODEL], 1ull );
 }
 
 /* the faces k_faces left waiting for an earlier face's clip point (a few per view): a warp per face - the lanes look at
@@ -671,6 +699,7 @@ struct Dev
 	rc_cmd2d_t *d_cmds2d = nullptr;
 	int32_t *d_pairs = nullptr; size_t cap_pairs = 0; int fast_maxcount = 0;
 	rc_bent_t *d_bents = nullptr; int32_t *d_bfaces = nullptr; int nbents = 0, nbfaces = 0;
+	int32_t *d_leafkey = nullptr, *d_tbord = nullptr, *d_tbcounts = nullptr; rc_surf_t *d_tbsurfs = nullptr; rc_edge_t *d_tbedges = nullptr; int ntb = 0; size_t cap_tb = 0;
 	int32_t *d_leafbase = nullptr, *d_viewbm = nullptr; uint32_t *d_bmvis = nullptr; size_t cap_leafbase = 0, cap_bmvis = 0, cap_viewbm = 0;
 	int32_t *d_partbox = nullptr; size_t cap_partbox = 0; uint8_t *d_itemvis = nullptr; size_t cap_itemvis = 0;
 	int32_t *d_item_order = nullptr; rc_poly_t *d_polys = nullptr;
@@ -902,6 +931,11 @@ rc_work_t make_slice( int k, int v0, int v1 )
 	ws.pairs = D.d_pairs ? D.d_pairs + (size_t)v0 * ( D.nfast_items > 0 ? D.nfast_items : 1 ) : nullptr;
 	ws.bents = D.d_bents; ws.nbents = D.nbents; ws.bfaces = D.d_bfaces; ws.nbfaces = D.nbfaces;
 	ws.leafbase = D.d_leafbase ? D.d_leafbase + (size_t)v0 * sc.numleafs : nullptr;
+	ws.leafkey = D.d_leafkey ? D.d_leafkey + (size_t)v0 * sc.numleafs : nullptr;
+	ws.tbord = D.d_tbord; ws.ntb = D.ntb;
+	ws.tb_surfs = D.d_tbsurfs ? D.d_tbsurfs + (size_t)v0 * D.ntb * RC_TB_MAXSURFS : nullptr;
+	ws.tb_edges = D.d_tbedges ? D.d_tbedges + (size_t)v0 * D.ntb * RC_TB_MAXEDGES : nullptr;
+	ws.tb_counts = D.d_tbcounts ? D.d_tbcounts + (size_t)v0 * D.ntb * 2 : nullptr;
 	ws.viewbm = D.d_viewbm ? D.d_viewbm + v0 : nullptr;
 	ws.bmvis = D.d_bmvis ? D.d_bmvis + (size_t)v0 * ( ws.nodewords + ws.leafwords ) : nullptr;
 	ws.partbox = D.d_partbox; ws.itemvis = D.d_itemvis ? D.d_itemvis + (size_t)v0 * D.nitems : nullptr;
@@ -950,6 +984,11 @@ int launch_slice( const rc_work_t &ws, int k, cudaStream_t st, cudaEvent_t *evs,
 			k_bmodels<<<gb, 64, 0, st>>>( sc, ws ); D.launches++;
 			KCHECK( "k_bmodels", st );
 		}
+		if( D.ntb )
+		{
+			k_tbrush_pieces<<<( ws.nviews * D.nbents + 63 ) / 64, 64, 0, st>>>( sc, ws ); D.launches++;
+			KCHECK( "k_tbrush_pieces", st );
+		}
 	}
 	if( evs ) CK( cudaEventRecord( evs[2], st ));
 	{
@@ -986,7 +1025,7 @@ int launch_slice( const rc_work_t &ws, int k, cudaStream_t st, cudaEvent_t *evs,
 		D.launches++;
 		KCHECK( "k_draw", st );
 		if( evs ) CK( cudaEventRecord( evs[5], st ));
-		if( D.nitems && D.ntris )
+		if( D.nitems && ( D.ntris || D.ntb ))
 		{
 			/* entities: after the world's spans are in the frame (R_DrawEntitiesOnList follows R_EdgeDrawing, r_main.c:1090) */
 			if( launch_studio_points( st ) != 0 ) return -1;
@@ -1003,11 +1042,14 @@ int launch_slice( const rc_work_t &ws, int k, cudaStream_t st, cudaEvent_t *evs,
 				KCHECK( "k_tri_resolve", st );
 			}
 			const int nord = D.ntris - D.fast_tris;
-			if( nord > 0 )
+			if( nord > 0 || D.ntb )
 			{
 				k_item_order<<<ws.nviews, 128, 0, st>>>( ws ); D.launches++;
-				dim3 gp(( nord + 127 ) / 128, ws.nviews );
-				k_tri_polys<<<gp, 128, 0, st>>>( ws, nord ); D.launches++;
+				if( nord > 0 )
+				{
+					dim3 gp(( nord + 127 ) / 128, ws.nviews );
+					k_tri_polys<<<gp, 128, 0, st>>>( ws, nord ); D.launches++;
+				}
 				dim3 gt( ws.nviews, TR_STRIPS );
 				k_tris_ordered<<<gt, TR_THREADS, 0, st>>>( sc, ws, nord ); D.launches++;
 			}
@@ -1112,7 +1154,7 @@ void rc_dev_shutdown( void )
 	cudaDeviceSynchronize();
 	free_batch();
 	/* everything rc_dev_init / the uploads created, so that R_Shutdown + R_Init (vid_restart) starts clean */
-	void **ptrs[] = { (void **)&D.d_bents, (void **)&D.d_bfaces, (void **)&D.d_leafbase, (void **)&D.d_viewbm, (void **)&D.d_bmvis, (void **)&D.d_pairs, (void **)&D.d_partbox, (void **)&D.d_itemvis, (void **)&D.d_cmds2d, (void **)&D.d_trikeys, (void **)&D.d_biglist, (void **)&D.d_sstatic, (void **)&D.d_parts, (void **)&D.d_bones, (void **)&D.d_blight, (void **)&D.d_mvpos, (void **)&D.d_mlight, (void **)&D.d_item_order, (void **)&D.d_polys, (void **)&D.d_alphamap, (void **)&D.d_addmap, (void **)&D.d_modmap, (void **)&D.d_items, (void **)&D.d_corners, (void **)&D.d_sortents, (void **)&D.d_display, (void **)&D.d_screenmap, (void **)&D.d_dlights, (void **)&D.d_dlightbits,
+	void **ptrs[] = { (void **)&D.d_leafkey, (void **)&D.d_tbord, (void **)&D.d_tbcounts, (void **)&D.d_tbsurfs, (void **)&D.d_tbedges, (void **)&D.d_bents, (void **)&D.d_bfaces, (void **)&D.d_leafbase, (void **)&D.d_viewbm, (void **)&D.d_bmvis, (void **)&D.d_pairs, (void **)&D.d_partbox, (void **)&D.d_itemvis, (void **)&D.d_cmds2d, (void **)&D.d_trikeys, (void **)&D.d_biglist, (void **)&D.d_sstatic, (void **)&D.d_parts, (void **)&D.d_bones, (void **)&D.d_blight, (void **)&D.d_mvpos, (void **)&D.d_mlight, (void **)&D.d_item_order, (void **)&D.d_polys, (void **)&D.d_alphamap, (void **)&D.d_addmap, (void **)&D.d_modmap, (void **)&D.d_items, (void **)&D.d_corners, (void **)&D.d_sortents, (void **)&D.d_display, (void **)&D.d_screenmap, (void **)&D.d_dlights, (void **)&D.d_dlightbits,
 		(void **)&D.d_colormap, (void **)&D.d_lightgamma, (void **)&D.d_sintable, (void **)&D.d_textures, (void **)&D.d_texels,
 		(void **)&D.d_styles, (void **)&D.d_keys, (void **)&D.d_need, (void **)&D.d_list, (void **)&D.d_nlist,
 		(void **)&D.d_counters, &D.d_flush };
@@ -1122,7 +1164,7 @@ void rc_dev_shutdown( void )
 	D.cap_cands = D.cap_edges = D.cap_blk_events = 0; D.caps_dirty = false;
 	D.nitems = D.ncorners = D.nsortents = 0; D.h_items.clear(); D.ntris = 0; D.cap_item_order = D.cap_polys = 0;
 	D.nparts = D.totalverts = D.totalnorms = 0; D.cap_mvpos = D.cap_mlight = 0; D.studio_dirty = false;
-	D.nfast_items = D.fast_tris = 0; D.cap_trikeys = D.cap_big = 0; D.cap_partbox = D.cap_itemvis = D.cap_pairs = 0; D.nbents = D.nbfaces = 0; D.cap_leafbase = D.cap_bmvis = D.cap_viewbm = 0;
+	D.nfast_items = D.fast_tris = 0; D.cap_trikeys = D.cap_big = 0; D.cap_partbox = D.cap_itemvis = D.cap_pairs = 0; D.nbents = D.nbfaces = 0; D.cap_leafbase = D.cap_bmvis = D.cap_viewbm = 0; D.ntb = 0; D.cap_tb = 0;
 	D.display_bytes = 0; D.ndlights = 0; D.screen_bpp = 0; D.cache_texels = 0; D.ntextures = 0;
 	D.sc = rc_scene_t{}; D.h_surfaces.clear(); D.h_textures.clear();
 	cudaStream_t *streams[] = { &D.stream, &D.copy };
@@ -1287,7 +1329,7 @@ int rc_dev_set_items( const rc_item_t *items, int nitems, const rc_corner_t *cor
 int rc_dev_set_bents( const rc_bent_t *bents, int n )
 {
 	if( n > RC_MAX_BENTS ) n = RC_MAX_BENTS;
-	D.nbents = 0; D.nbfaces = 0;
+	D.nbents = 0; D.nbfaces = 0; D.ntb = 0;
 	if( n <= 0 ) return 0;
 	std::vector<int32_t> bf;
 	for( int e = 0; e < n; e++ )
@@ -1295,6 +1337,11 @@ int rc_dev_set_bents( const rc_bent_t *bents, int n )
 	if( upload( &D.d_bents, bents, (size_t)n ) != 0 ) return -1;
 	if( upload( &D.d_bfaces, bf.data(), bf.size()) != 0 ) return -1;
 	D.h2d_bytes += sizeof( rc_bent_t ) * (size_t)n + 4 * bf.size();
+	std::vector<int32_t> ord( n );
+	int ntb = 0;
+	for( int e = 0; e < n; e++ ) ord[e] = bents[e].trans ? ntb++ : -1;
+	if( upload( &D.d_tbord, ord.data(), ord.size()) != 0 ) return -1;
+	D.ntb = ntb;
 	D.nbents = n; D.nbfaces = (int)bf.size();
 	return 0;
 }
@@ -1404,11 +1451,17 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 		if( D.nbents )
 		{
 			const size_t need_l = (size_t)D.cap_views * D.sc.numleafs, need_b = (size_t)D.cap_views * ( D.w.nodewords + D.w.leafwords );
-			if( need_l > D.cap_leafbase ) { if( dalloc( &D.d_leafbase, need_l ) != 0 ) return -1; D.cap_leafbase = need_l; }
+			if( need_l > D.cap_leafbase ) { if( dalloc( &D.d_leafbase, need_l ) != 0 || dalloc( &D.d_leafkey, need_l ) != 0 ) return -1; D.cap_leafbase = need_l; }
+			const size_t need_t = (size_t)D.cap_views * D.ntb;
+			if( need_t > D.cap_tb )
+			{
+				if( dalloc( &D.d_tbsurfs, need_t * RC_TB_MAXSURFS ) != 0 || dalloc( &D.d_tbedges, need_t * RC_TB_MAXEDGES ) != 0 || dalloc( &D.d_tbcounts, need_t * 2 ) != 0 ) return -1;
+				D.cap_tb = need_t;
+			}
 			if( need_b > D.cap_bmvis ) { if( dalloc( &D.d_bmvis, need_b ) != 0 ) return -1; D.cap_bmvis = need_b; }
 			if( (size_t)D.cap_views > D.cap_viewbm ) { if( dalloc( &D.d_viewbm, (size_t)D.cap_views ) != 0 ) return -1; D.cap_viewbm = D.cap_views; }
 		}
-		if( D.nitems && D.ntris )
+		if( D.nitems && ( D.ntris || D.ntb ))
 		{
 			const size_t need_v = (size_t)D.cap_views * D.nitems;
 			if( need_v > D.cap_itemvis ) { if( dalloc( &D.d_itemvis, need_v ) != 0 ) return -1; D.cap_itemvis = need_v; }

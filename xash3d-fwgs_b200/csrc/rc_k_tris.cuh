@@ -251,10 +251,80 @@ __global__ void __launch_bounds__( 128 ) k_tri_polys( rc_work_t w, int32_t ntris
 	}
 }
 
+/*
+ * A translucent brush entity in its turn (R_DrawBrushModel's R_ScanEdges + D_AlphaSurf): the warps of the block take the
+ * strip's scanlines 32 at a time.  Lane = scanline: the line's events out of the entity's edges, sorted, through the span
+ * generator (rc_tbrush_line) into shared memory; then line by line, lane = 8-pixel (16 for water) subdivision of a span:
+ * the reference's float chain to the subdivision (rc_chunk_setup), its pixels through D_AlphaSpans16 / D_BlendSpans16 /
+ * D_AddSpans16 / D_DrawTurbulent8ZSpan (rc_alpha_pixel).  A pixel belongs to one span of the frame: no two lanes meet.
+ */
+__device__ __forceinline__ void rc_tbrush_draw( const rc_scene_t &sc, const rc_work_t &w, const rc_blendluts_t *L, int view, int32_t ent,
+	int32_t ys0, int32_t ys1, uint16_t *color, int16_t *zb, rc_span_t *spans, int32_t *nspans, int lane, int warp )
+{
+	const int32_t tb = w.tbord[ent];
+	if( tb < 0 )
+		return;
+	const size_t slot = (size_t)view * w.ntb + tb;
+	const int32_t ns = w.tb_counts[2 * slot], nedges = w.tb_counts[2 * slot + 1];
+	if( ns <= 0 || nedges <= 0 )
+		return;
+	const rc_bent_t *be = &w.bents[ent];
+	const rc_surf_t *surfs = w.tb_surfs + slot * RC_TB_MAXSURFS;
+	const rc_edge_t *edges = w.tb_edges + slot * RC_TB_MAXEDGES;
+	const rc_view_t *vw = &w.views[view];
+	const int32_t *turb = sc.sintable + vw->turb_phase;
+	const int32_t x0 = vw->vrect[0], vy0 = vw->vrect[1], vy1 = vw->vrect[1] + vw->vrect[3];
+	const int32_t head_iu = x0, tail_u = (( x0 + vw->vrect[2] ) << 20 ) + 0xFFFFF;
+	const int32_t ya = max( ys0, vy0 ), yb = min( ys1, vy1 );
+	const uint32_t alpha = (uint32_t)min( be->alpha, 7 );
+	for( int32_t yg = ya + warp * 32; yg < yb; yg += ( TR_THREADS / 32 ) * 32 )
+	{
+		const int32_t y = yg + lane;
+		int32_t n = 0, ovf = 0;
+		if( y < yb )
+			n = rc_tbrush_line( surfs, edges, nedges, y, head_iu, tail_u, spans + lane * RC_TB_LINESPANS, RC_TB_LINESPANS, &ovf );
+		nspans[lane] = n;
+		if( ovf ) atomicAdd( &w.counters[RC_CTR_OVERFLOW_EVENTS], 1ull );
+		__syncwarp();
+		for( int32_t ln = 0; ln < 32 && yg + ln < yb; ln++ )
+		{
+			const int32_t yl = yg + ln;
+			for( int32_t si = 0; si < nspans[ln]; si++ )
+			{
+				const rc_span_t sp = spans[ln * RC_TB_LINESPANS + si];
+				if( !sp.surf )
+					continue;
+				const rc_surf_t *sf = &surfs[sp.surf - 1];
+				const int32_t kind = rc_span_kind( sf );
+				if( kind == RC_KIND_SKY || ( kind == RC_KIND_TURB && alpha == 0 ))
+					continue;
+				const int32_t nch = rc_span_nchunks( kind, sp.count ), cpx = kind == RC_KIND_TURB ? 16 : 8;
+				for( int32_t j = lane; j < nch; j += 32 )
+				{
+					rc_chunk_t c;
+					rc_chunk_setup( vw, sf, vw->sky_color, sp.u, yl, sp.count, j, &c );
+					const int32_t npx = min( cpx, sp.count - j * cpx );
+					const size_t base = (size_t)yl * w.width + c.u0;
+					for( int32_t i = 0; i < npx; i++ )
+					{
+						const int32_t ti = rc_pixel_texel( &c, i, turb );
+						const uint32_t texel = kind == RC_KIND_TURB ? __ldg( sc.texels + ti ) : sc.cache[ti];
+						const int32_t izi = (int32_t)((uint32_t)c.izi + (uint32_t)i * (uint32_t)c.izistep );
+						rc_alpha_pixel( L, be->trans, alpha, kind == RC_KIND_TURB, texel, izi, &color[base + i], &zb[base + i] );
+					}
+				}
+			}
+		}
+		__syncwarp();
+	}
+}
+
 __global__ void __launch_bounds__( TR_THREADS ) k_tris_ordered( rc_scene_t sc, rc_work_t w, int32_t ntris )
 {
 	__shared__ rc_trisetup_t s_ts;
 	__shared__ int32_t s_go, s_y0, s_rows;
+	__shared__ rc_span_t s_tbspans[TR_THREADS / 32][32 * RC_TB_LINESPANS];
+	__shared__ int32_t s_tbn[TR_THREADS / 32][32];
 	const int view = blockIdx.x, strip = blockIdx.y, t = threadIdx.x, lane = t & 31, warp = t >> 5;
 	const int32_t ys0 = (int32_t)((long long)w.height * strip / gridDim.y ), ys1 = (int32_t)((long long)w.height * ( strip + 1 ) / gridDim.y );
 	uint16_t *color = w.color + (size_t)view * w.width * w.height;
@@ -273,6 +343,12 @@ __global__ void __launch_bounds__( TR_THREADS ) k_tris_ordered( rc_scene_t sc, r
 		const rc_item_t *it = &w.items[idx];
 		if( it->tex_ofs < 0 || idx < w.nfast_items )
 			continue;
+		if( it->kind == RC_ITEM_BRUSH )
+		{
+			__syncthreads(); /* the previous item's pixels are in the frame */
+			rc_tbrush_draw( sc, w, &L, view, it->first, ys0, ys1, color, zb, s_tbspans[warp], s_tbn[warp], lane, warp );
+			continue;
+		}
 		const uint16_t *skin = sc.texels + it->tex_ofs;
 		const int32_t drawer = it->drawer;
 		const uint32_t icolor = (uint32_t)it->color, ialpha = (uint32_t)it->alpha;

@@ -491,6 +491,7 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 			const int32_t e = leaflist[k], leaf = -1 - e_ref[e], pos = e_pos[e];
 			const int32_t base = seq[pos], n = ( pos + 1 < nseq ? seq[pos + 1] : total ) - base;
 			leafbase[leaf] = base;
+			if( w.leafkey ) w.leafkey[(size_t)view * sc.numleafs + leaf] = pos; /* the leaf's place in the walk: translucent brush entities key their pieces by it */
 			for( int32_t o = base; o < base + n && o < w.max_cands; o++ ) { cands[o].surf = -1; cands[o].clipflags = 0; }
 		}
 		/* R_FindTopnode and R_RecursiveClipBPoly test node / leaf visframe: the PVS marks leave the block */

@@ -332,6 +332,14 @@ def add_brush_entities(r, m, cams, count=16, ahead=88.0, drop=24.0, rotate=True,
         r.add_entity(models[k % len(models)]["modelindex"], org, angles=ang, rendermode=rendermode, renderamt=renderamt)
 
 
+def add_mixed_brush_entities(r, m, cams):
+    """opaque, blended (kRenderTransTexture), additive and alpha-tested brush entities in front of the first 26 cameras"""
+    add_brush_entities(r, m, cams, 8, rotate=True)
+    add_brush_entities(r, m, cams[8:], 6, rotate=True, rendermode=2, renderamt=140)
+    add_brush_entities(r, m, cams[14:], 6, rotate=False, rendermode=5, renderamt=200)
+    add_brush_entities(r, m, cams[20:], 6, rotate=True, rendermode=4, renderamt=255)
+
+
 def sprite_image(seed, w=64, h=64):
     """a synthetic RGBA sprite frame: a soft disc with noise, transparent outside"""
     rng = np.random.default_rng(seed)
