@@ -49,6 +49,19 @@ REF_CUDA_EXPORT int RefCuda_RenderViews( const struct ref_viewpass_s *views, int
 REF_CUDA_EXPORT int RefCuda_BlitViews( int first, int nviews, void *dst, unsigned int stride, unsigned int bpp,
 	unsigned int rmask, unsigned int gmask, unsigned int bmask, float *ms_kernel );
 
+/*
+ * No counterpart in the reference.  RefCuda_BlitViews' conversion kernel for
+ * callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc): converts
+ * npixels pixel_t codes (host memory) to the display format (bpp 2 or 4 and the three channel masks, as above) into dst
+ * (host memory, npixels * bpp bytes).  Screen map, input and output are staged in a file-scope device array inside the
+ * library (~12.7 MB per GPU that loads it, held until exit) - the call makes no cudaMalloc / cudaFree and no host
+ * allocation.  Limit: npixels <= 2 073 600 (one 1920x1080 frame); more returns -2 with a message on the engine console.
+ * The array is shared by all calls and keeps the last call's contents: calls that overlap on the GPU (several threads)
+ * race; serialise them.  Works on the calling thread's current CUDA device.  Returns 0 on success.
+ */
+REF_CUDA_EXPORT int RefCuda_BlitPixelsNoAlloc( const unsigned short *pixels, unsigned int npixels, void *dst, unsigned int bpp,
+	unsigned int rmask, unsigned int gmask, unsigned int bmask );
+
 /* Re-run the device stages of the last batch with all inputs resident in HBM; CUDA-event milliseconds
  * per iteration: total and per stage, ms_stage[6] = [visibility+BSP walk, face/edge set-up, surface cache,
  * span generation, span drawing, entities (studio skinning + triangle rasteriser)].

@@ -606,6 +606,7 @@ int rc_dev_set_dlights( const rc_dlight_t *, int n ) { return n ? -1 : 0; }
 int rc_dev_set_screenmap( const uint32_t *, int ) { return 0; }
 int rc_dev_set_bents( const rc_bent_t *bents, int n ) { E.bents.assign( bents, bents + ( n > 0 ? n : 0 )); return 0; }
 int rc_dev_draw2d( const rc_cmd2d_t *, int, int ) { snprintf( E.err, sizeof( E.err ), "HUD pass: not in the debug harness" ); return -1; }
+int rc_dev_blit_static( const uint32_t *, int, const uint16_t *, size_t, void * ) { snprintf( E.err, sizeof( E.err ), "display tail: not in the debug harness" ); return -1; }
 int rc_dev_blit( int, int, void *, size_t, float * ) { snprintf( E.err, sizeof( E.err ), "display tail: not in the debug harness" ); return -1; }
 
 int rc_dev_bench_resident( int, int, float *ms_total, float *ms_stage )

@@ -70,6 +70,10 @@ int rc_dev_bench_resident( int iters, int flags, float *ms_total, float *ms_stag
  * ms_kernel (optional): CUDA-event time of the conversion kernel */
 int rc_dev_set_screenmap( const uint32_t *table, int bpp );
 int rc_dev_blit( int first, int nviews, void *dst, size_t stride, float *ms_kernel );
+/* k_blit over a fixed file-scope device array instead of allocated buffers: table = the 65536-entry screen map, pixels =
+ * npx pixel_t codes (host), dst = npx display pixels of bpp bytes (host).  Allocates nothing; npx <= RC_STATIC_BLIT_MAXPX. */
+#define RC_STATIC_BLIT_MAXPX ( 1920 * 1080 )
+int rc_dev_blit_static( const uint32_t *table, int bpp, const uint16_t *pixels, size_t npx, void *dst );
 
 /* probes for the parity tests */
 int rc_dev_read_cache_block( int surf, int mip, uint16_t *out, int maxtexels, int *width, int *height, int *valid );

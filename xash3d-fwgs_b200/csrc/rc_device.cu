@@ -1615,6 +1615,64 @@ int rc_dev_blit( int first, int nviews, void *dst, size_t stride, float *ms_kern
 	return 0;
 }
 
+/* ---------------------------------------------------------------------------------------------- */
+/* k_blit without an allocation (RefCuda_BlitPixelsNoAlloc, include/ref_cuda.h).
+ *
+ * rc_dev_blit keeps its screen map and its output staging buffer in cudaMalloc'ed memory.  Callers that must not allocate
+ * (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc) get the same kernel over a file-scope device
+ * array of a fixed size: the 256 KB screen map, the frame's pixel_t codes and the converted frame.  Every GPU that loads the
+ * library holds the array (RC_STATIC_BLIT_BYTES, ~12.7 MB) until exit.  All calls share it and it keeps the last call's
+ * contents; nothing in it has to start at zero (the table and the input are written before the kernel reads them, the
+ * kernel writes every output pixel the copy-out reads).  Calls that overlap on the GPU (other threads, other streams) race.
+ *
+ * In host code g_static_blit is a host-side stand-in for the symbol, not a device address: the address the kernel gets
+ * comes from cudaGetSymbolAddress, resolved once per device with that device current.                                   */
+
+struct rc_static_blit_t
+{
+	uint32_t lut[65536];                    /* R_BuildScreenMap's table for the call's display format */
+	uint16_t in[RC_STATIC_BLIT_MAXPX];      /* pixel_t codes */
+	uint32_t out[RC_STATIC_BLIT_MAXPX];     /* display pixels (bpp 2: the first half is used) */
+};
+#define RC_STATIC_BLIT_BYTES sizeof( rc_static_blit_t )
+static __device__ __align__( 256 ) unsigned char g_static_blit[RC_STATIC_BLIT_BYTES];
+#define RC_STATIC_MAXDEV 64
+static rc_static_blit_t *g_static_blit_ptr[RC_STATIC_MAXDEV]; /* device address of g_static_blit on every device that asked */
+
+int rc_dev_blit_static( const uint32_t *table, int bpp, const uint16_t *pixels, size_t npx, void *dst )
+{
+	if( !table || !pixels || !dst || ( bpp != 2 && bpp != 4 )) { snprintf( D.err, sizeof( D.err ), "rc_dev_blit_static: bad arguments (bpp must be 2 or 4)" ); return -1; }
+	if( npx == 0 ) return 0;
+	if( npx > RC_STATIC_BLIT_MAXPX )
+	{
+		snprintf( D.err, sizeof( D.err ), "rc_dev_blit_static: %zu pixels, the static scratch holds %d (one 1920x1080 frame)", npx, RC_STATIC_BLIT_MAXPX );
+		return -1;
+	}
+	int dev = -1;
+	CK( cudaGetDevice( &dev ));
+	if( dev < 0 || dev >= RC_STATIC_MAXDEV ) { snprintf( D.err, sizeof( D.err ), "rc_dev_blit_static: device ordinal %d out of range", dev ); return -1; }
+	if( !g_static_blit_ptr[dev] )
+	{
+		/* set-up, once per device, with that device current */
+		void *p = nullptr;
+		CK( cudaGetSymbolAddress( &p, g_static_blit ));
+		if( !p ) { snprintf( D.err, sizeof( D.err ), "rc_dev_blit_static: cudaGetSymbolAddress returned no address" ); return -1; }
+		g_static_blit_ptr[dev] = reinterpret_cast<rc_static_blit_t *>( p );
+	}
+	rc_static_blit_t *sb = g_static_blit_ptr[dev];
+	/* default stream, synchronous copies: no stream, event or buffer is created here */
+	CK( cudaMemcpy( sb->lut, table, sizeof( uint32_t ) * 65536, cudaMemcpyHostToDevice ));
+	CK( cudaMemcpy( sb->in, pixels, npx * sizeof( uint16_t ), cudaMemcpyHostToDevice ));
+	const size_t want = ( npx / 8 + 255 ) / 256;
+	const int grid = (int)( want < 148 * 8 ? ( want ? want : 1 ) : 148 * 8 );
+	if( bpp == 2 ) k_blit<2><<<grid, 256>>>( sb->in, sb->lut, sb->out, npx );
+	else k_blit<4><<<grid, 256>>>( sb->in, sb->lut, sb->out, npx );
+	D.launches++;
+	CK( cudaGetLastError());
+	CK( cudaMemcpy( dst, sb->out, npx * (size_t)bpp, cudaMemcpyDeviceToHost ));
+	return 0;
+}
+
 int rc_dev_read_counters( uint64_t *out, int n )
 {
 	unsigned long long h[RC_CTR_COUNT];

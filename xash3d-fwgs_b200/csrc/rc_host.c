@@ -2185,6 +2185,29 @@ int RefCuda_BlitViews( int first, int nviews, void *dst, unsigned int stride, un
 	return rc_dev_blit( first, nviews, dst, stride, ms_kernel );
 }
 
+/* see include/ref_cuda.h: the display conversion over the library's static device scratch - no cudaMalloc, no host malloc */
+int RefCuda_BlitPixelsNoAlloc( const unsigned short *pixels, unsigned int npixels, void *dst, unsigned int bpp, unsigned int rmask, unsigned int gmask, unsigned int bmask )
+{
+	static uint32_t table[65536]; /* the call's screen map (256 KB, static: nothing is allocated on the host either) */
+	if( !pixels || !dst || ( bpp != 2 && bpp != 4 ))
+	{
+		gEngfuncs.Con_Printf( S_ERROR "ref_cuda: RefCuda_BlitPixelsNoAlloc: bad arguments (bpp must be 2 or 4)\n" );
+		return -1;
+	}
+	if( npixels > RC_STATIC_BLIT_MAXPX )
+	{
+		gEngfuncs.Con_Printf( S_ERROR "ref_cuda: RefCuda_BlitPixelsNoAlloc: %u pixels requested, the static scratch holds at most %d (one 1920x1080 frame)\n", npixels, RC_STATIC_BLIT_MAXPX );
+		return -2;
+	}
+	rc_build_screenmap( table, rmask, gmask, bmask );
+	if( rc_dev_blit_static( table, (int)bpp, pixels, npixels, dst ) != 0 )
+	{
+		gEngfuncs.Con_Printf( S_ERROR "ref_cuda: RefCuda_BlitPixelsNoAlloc: %s\n", rc_dev_last_error());
+		return -1;
+	}
+	return 0;
+}
+
 int RefCuda_GetCounters( unsigned long long *out, int n ) { return rc_dev_read_counters((uint64_t *)out, n ); }
 unsigned long long RefCuda_LaunchCount( void ) { return rc_dev_launch_count(); }
 unsigned long long RefCuda_BatchH2DBytes( void ) { return rc.last_h2d; }
