@@ -3,8 +3,9 @@
  * a submodule that is absent from the mounted reference tree (.SUBMODULES.json).
  * The reference only needs the platform switches below on this box
  * (x86-64 Linux, little endian); every other XASH_* test defaults to 0.
- * TEST INFRASTRUCTURE: used only to compile the unmodified reference ref_soft
- * into oracle/_ref/ and to read the engine's SDK headers; never shipped.
+ * Needed by everything that reads the engine's SDK headers (port.h includes "build.h"): the plugin's host side
+ * (rc_host.c), the headless engine stand-in (harness/) and the oracle build of the unmodified reference ref_soft.
+ * Inside the engine's own tree the real 3rdparty/library_suffix/build.h takes its place.
  */
 #pragma once
 #ifndef BUILD_H

@@ -100,10 +100,25 @@ int rc_dev_upload_luts( const uint16_t *colormap, const uint16_t *lightgamma, co
 	return 0;
 }
 
-int rc_dev_upload_textures( const rc_texture_t *tex, int ntex, const uint16_t *texels, size_t ntexels )
+int rc_dev_upload_textures( const rc_texture_t *tex, const rc_texsrc_t *src, int ntex, const uint32_t *rgba, size_t, size_t ntexels )
 {
 	E.textures.assign( tex, tex + ntex );
-	E.texels.assign( texels, texels + ntexels );
+	E.texels.assign( ntexels, 0 );
+	/* k_tex_encode, sequentially: every plane of every texture, texel by texel */
+	for( int i = 0; i < ntex; i++ )
+	{
+		const rc_texture_t &t = tex[i];
+		if( t.ofs[0] < 0 ) continue;
+		for( int plane = 0; plane < 5; plane++ )
+		{
+			const int level = plane == 4 ? 0 : plane;
+			const int32_t ofs = plane == 4 ? t.alpha_ofs : t.ofs[plane];
+			if( ofs < 0 ) continue;
+			const int32_t n = std::max( 1, t.width >> level ) * std::max( 1, t.height >> level );
+			for( int32_t k = 0; k < n; k++ )
+				E.texels[(size_t)ofs + k] = rc_tex_encode( rgba + src[i].rgba_ofs, t.width, t.height, src[i].flags, plane, k );
+		}
+	}
 	fix_pointers();
 	return rc_dev_flush_cache();
 }

@@ -154,6 +154,84 @@ RC_HD void rc_mark_leaves( const rc_scene_t *sc, const uint8_t *vis, uint32_t *n
 }
 
 /* ------------------------------------------------------------------------------------------ */
+/* A19: texture encode - GL_UploadTexture + GL_BuildMipMap (ref/soft/r_image.c:214-283,125-207) per output texel.
+ * The reference box-filters the RGBA image in place, level after level (each level rounds: ( a + b + c + d ) >> 2), and
+ * encodes every level to pixel_t.  A texel of level j is therefore a fixed tree of averages over a 2^j x 2^j block of the
+ * source - evaluated here on its own, so that every output texel of every level is independent (one thread each).      */
+
+/* pixel_t code of an RGB triple already reduced to 5/6/5 bits: major RGB332 << 8 | minor GBRGBRGB (r_image.c:261-271) */
+RC_HD uint32_t rc_pixel_encode( uint32_t r, uint32_t g, uint32_t b )
+{
+	const uint32_t major = ((( r >> 2 ) & 7u ) << 5 ) | ((( g >> 3 ) & 7u ) << 2 ) | (( b >> 3 ) & 3u );
+	const uint32_t minor = ((( r >> 1 ) & 1u ) << 5 ) | (( r & 1u ) << 2 )
+		| ((( g >> 2 ) & 1u ) << 7 ) | ((( g >> 1 ) & 1u ) << 4 ) | (( g & 1u ) << 1 )
+		| ((( b >> 2 ) & 1u ) << 6 ) | ((( b >> 1 ) & 1u ) << 3 ) | ( b & 1u );
+	return ( major << 8 | minor ) & 0xFFFFu;
+}
+
+/* one output texel of GL_BuildMipMap's box filter from the (up to) four texels of the level below it */
+RC_HD uint32_t rc_tex_box( uint32_t a, uint32_t b, uint32_t c, uint32_t d, int two_x )
+{
+	uint32_t out = 0;
+	if( two_x )
+		for( int k = 0; k < 32; k += 8 )
+			out |= (((( a >> k ) & 255u ) + (( b >> k ) & 255u ) + (( c >> k ) & 255u ) + (( d >> k ) & 255u )) >> 2 ) << k;
+	else
+		for( int k = 0; k < 32; k += 8 )
+			out |= (((( a >> k ) & 255u ) + (( c >> k ) & 255u )) >> 1 ) << k;
+	return out;
+}
+
+/* the RGBA value (packed, R in the low byte) GL_BuildMipMap leaves at (x, y) of a level; W, H: level-0 size.  A texel
+ * averages its 2 x 2 block of the level below; a level of width (height) 1 has no second column (row): r_image.c:150-175.
+ * One function per level (no recursion on the device). */
+#define RC_TEX_LEVEL( NAME, BELOW, LEVEL ) \
+RC_HD uint32_t NAME( const uint32_t *src, int32_t W, int32_t H, int32_t x, int32_t y ) \
+{ \
+	int32_t sw = W >> (( LEVEL ) - 1 ), sh = H >> (( LEVEL ) - 1 ); \
+	if( sw < 1 ) sw = 1; \
+	if( sh < 1 ) sh = 1; \
+	const int two_x = ( 2 * x + 1 ) < sw, two_y = ( 2 * y + 1 ) < sh; \
+	const uint32_t a = BELOW( src, W, H, 2 * x, 2 * y ); \
+	const uint32_t c = two_y ? BELOW( src, W, H, 2 * x, 2 * y + 1 ) : a; \
+	const uint32_t b = two_x ? BELOW( src, W, H, 2 * x + 1, 2 * y ) : 0u; \
+	const uint32_t d = two_x ? ( two_y ? BELOW( src, W, H, 2 * x + 1, 2 * y + 1 ) : b ) : 0u; \
+	return rc_tex_box( a, b, c, d, two_x ); \
+}
+RC_HD uint32_t rc_tex_rgba0( const uint32_t *src, int32_t W, int32_t H, int32_t x, int32_t y ) { (void)H; return src[(size_t)y * W + x]; }
+RC_TEX_LEVEL( rc_tex_rgba1, rc_tex_rgba0, 1 )
+RC_TEX_LEVEL( rc_tex_rgba2, rc_tex_rgba1, 2 )
+RC_TEX_LEVEL( rc_tex_rgba3, rc_tex_rgba2, 3 )
+
+RC_HD uint32_t rc_tex_rgba( const uint32_t *src, int32_t W, int32_t H, int32_t level, int32_t x, int32_t y )
+{
+	switch( level )
+	{
+	case 0: return rc_tex_rgba0( src, W, H, x, y );
+	case 1: return rc_tex_rgba1( src, W, H, x, y );
+	case 2: return rc_tex_rgba2( src, W, H, x, y );
+	default: return rc_tex_rgba3( src, W, H, x, y );
+	}
+}
+
+/* texel i of plane `plane` of a texture: 0..3 = the mip levels, 4 = the alpha plane (level 0: pixel >> 3 | alpha3 << 13) */
+RC_HD uint16_t rc_tex_encode( const uint32_t *src, int32_t W, int32_t H, int32_t srcflags, int32_t plane, int32_t i )
+{
+	const int32_t level = plane == 4 ? 0 : plane;
+	int32_t lw = W >> level;
+	if( lw < 1 ) lw = 1;
+	const int32_t y = i / lw, x = i - y * lw;
+	const uint32_t v = rc_tex_rgba( src, W, H, level, x, y );
+	const uint32_t r = ( v & 255u ) * 32u / 256u, g = (( v >> 8 ) & 255u ) * 64u / 256u, b = (( v >> 16 ) & 255u ) * 32u / 256u, a = v >> 24;
+	const uint32_t px = rc_pixel_encode( r, g, b );
+	if( plane == 4 )
+		return (uint16_t)(( px >> 3 ) | (( a * 8u / 256u ) << 13 ));
+	if( plane == 0 && ( srcflags & RC_TEXSRC_COLORKEY ) && a < 128u )
+		return (uint16_t)0x0349; /* TRANSPARENT_COLOR */
+	return (uint16_t)px;
+}
+
+/* ------------------------------------------------------------------------------------------ */
 /* A2: front-to-back BSP walk                                                                   */
 
 /* the 4-plane bbox test of R_RecursiveWorldNode (ref/soft/r_bsp.c:483-520); returns -1 when rejected,
@@ -813,7 +891,6 @@ static inline int32_t rc_fetch_add_host( int32_t *p, int32_t n ) { const int32_t
 #endif
 
 #define RC_TOPNODE_NONE    ((int32_t)0x80000000 )
-#define RC_BACKFACE_EPSILON 0.01f
 #define RC_BM_MAXVERTS 56  /* per face: its own vertices + the points the BSP planes cut (the reference: 1000 per face) */
 #define RC_BM_MAXEDGES 112
 #define RC_BM_STACK    48

@@ -22,7 +22,10 @@ const char *rc_dev_name( void );
 /* static tables: colormap[32*8192] u16, lightgamma[1024] u16, sintable[1280] i32 */
 int rc_dev_upload_luts( const uint16_t *colormap, const uint16_t *lightgamma, const int32_t *sintable );
 /* texture table + texel arena (pixel_t), replaces the previous one */
-int rc_dev_upload_textures( const rc_texture_t *tex, int ntex, const uint16_t *texels, size_t ntexels );
+/* the texture table: tex[i] says where texture i's planes go in the pixel_t arena (ntexels long), src[i] where its RGBA8
+ * source sits in rgba[] (nrgba uint32).  The arena is ENCODED ON THE DEVICE (k_tex_encode: GL_UploadTexture +
+ * GL_BuildMipMap per output texel); textures with ofs[0] < 0 have no image */
+int rc_dev_upload_textures( const rc_texture_t *tex, const rc_texsrc_t *src, int ntex, const uint32_t *rgba, size_t nrgba, size_t ntexels );
 /* world arrays: sc holds HOST pointers and counts; cache_texels = size of the surface cache arena */
 int rc_dev_upload_scene( const rc_scene_t *sc, size_t cache_texels );
 /* texture number per surface after R_TextureAnimation (only changes when animated textures flip) */

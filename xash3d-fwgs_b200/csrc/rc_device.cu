@@ -1193,14 +1193,50 @@ int rc_dev_upload_luts( const uint16_t *colormap, const uint16_t *lightgamma, co
 	return rc_dev_flush_cache();
 }
 
-int rc_dev_upload_textures( const rc_texture_t *tex, int ntex, const uint16_t *texels, size_t ntexels )
+/* A19 on the device: block row = (texture, plane), threads stride over the plane's texels */
+__global__ void __launch_bounds__( 256 ) k_tex_encode( const rc_texture_t *tex, const rc_texsrc_t *src, const uint32_t *rgba, uint16_t *texels )
+{
+	const int ti = blockIdx.y / 5, plane = blockIdx.y - ti * 5;
+	const rc_texture_t t = tex[ti];
+	if( t.ofs[0] < 0 )
+		return;
+	const int level = plane == 4 ? 0 : plane;
+	const int32_t ofs = plane == 4 ? t.alpha_ofs : t.ofs[plane];
+	if( ofs < 0 )
+		return;
+	const int32_t n = max( 1, t.width >> level ) * max( 1, t.height >> level );
+	const rc_texsrc_t sr = src[ti];
+	const uint32_t *image = rgba + sr.rgba_ofs;
+	for( int32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x )
+		texels[(size_t)ofs + k] = rc_tex_encode( image, t.width, t.height, sr.flags, plane, k );
+}
+
+int rc_dev_upload_textures( const rc_texture_t *tex, const rc_texsrc_t *src, int ntex, const uint32_t *rgba, size_t nrgba, size_t ntexels )
 {
 	CK( cudaStreamSynchronize( D.stream ));
 	if( upload( &D.d_textures, tex, (size_t)ntex ) != 0 ) return -1;
-	if( upload( &D.d_texels, texels, ntexels ) != 0 ) return -1;
+	if( dalloc( &D.d_texels, ntexels ) != 0 ) return -1;
+	CK( cudaMemsetAsync( D.d_texels, 0, sizeof( uint16_t ) * ntexels, D.stream ));
 	D.h_textures.assign( tex, tex + ntex );
 	D.ntextures = ntex;
 	D.sc.textures = D.d_textures; D.sc.texels = D.d_texels; D.sc.numtextures = ntex;
+	if( ntex > 0 && nrgba > 0 )
+	{
+		/* the RGBA sources live on the device only while they are encoded */
+		rc_texsrc_t *d_src = nullptr; uint32_t *d_rgba = nullptr;
+		if( upload( &d_src, src, (size_t)ntex ) != 0 || upload( &d_rgba, rgba, nrgba ) != 0 ) { cudaFree( d_src ); cudaFree( d_rgba ); return -1; }
+		int32_t maxn = 1;
+		for( int i = 0; i < ntex; i++ ) if( tex[i].ofs[0] >= 0 && tex[i].width * tex[i].height > maxn ) maxn = tex[i].width * tex[i].height;
+		int bx = ( maxn + 255 ) / 256; if( bx > 64 ) bx = 64;
+		for( int t0 = 0; t0 < ntex; t0 += 8192 ) /* gridDim.y <= 65535 */
+		{
+			const int nt = ntex - t0 < 8192 ? ntex - t0 : 8192;
+			k_tex_encode<<<dim3( bx, nt * 5 ), 256, 0, D.stream>>>( D.d_textures + t0, d_src + t0, d_rgba, D.d_texels ); D.launches++;
+		}
+		cudaError_t e = cudaStreamSynchronize( D.stream );
+		cudaFree( d_src ); cudaFree( d_rgba );
+		if( e != cudaSuccess ) { snprintf( D.err, sizeof( D.err ), "k_tex_encode: %s", cudaGetErrorString( e )); return -1; }
+	}
 	return rc_dev_flush_cache();
 }
 

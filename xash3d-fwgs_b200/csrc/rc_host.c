@@ -70,9 +70,11 @@ typedef struct
 	char      name[256];
 	int       width, height, srcWidth, srcHeight;
 	uint      flags;
-	uint16_t *pixels[4];
-	uint16_t *alpha_pixels;
+	uint32_t *rgba;      /* the RGBA8 source as it was handed over: the device encodes pixel_t mips and the alpha plane from it */
+	qboolean  has_alpha; /* an alpha plane exists (TF_HAS_ALPHA): alpha_pixels of the reference */
+	qboolean  colorkey;  /* IMAGE_ONEBIT_ALPHA source and sw_noalphabrushes off when it was loaded */
 } rc_image_t;
+#define RC_IMAGE_LIVE( t ) (( t )->rgba != NULL )
 
 static struct
 {
@@ -227,162 +229,103 @@ static rc_image_t *rc_alloc_image( const char *name, uint flags )
 
 static void rc_delete_image( rc_image_t *tex )
 {
-	for( int i = 0; i < 4; i++ ) rc_free( tex->pixels[i] );
-	rc_free( tex->alpha_pixels );
+	rc_free( tex->rgba );
 	memset( tex, 0, sizeof( *tex ));
 	rc.textures_dirty = true;
 }
 
-/* box filter in place, quartering the image (the colour path of GL_BuildMipMap, r_image.c:125-207) */
-static void rc_build_mipmap( byte *in, int srcWidth, int srcHeight )
+/*
+ * Texture intake.  What GL_UploadTexture / GL_BuildMipMap do on the CPU in the reference (ref/soft/r_image.c:125-283: four
+ * box-filtered mips encoded to pixel_t, the alpha plane, the colour key) is a kernel here (k_tex_encode, rc_core.h A19): the
+ * host only keeps the RGBA8 source of every texture and, when the set changed, sends all sources in one arena
+ * (rc_sync_textures).  One routine serves the three loader slots of the interface.
+ */
+static qboolean rc_name_ok( const char *name )
 {
-	byte *out = in;
-	int instride = srcWidth * 4;
-	int mipWidth = Q_max( 1, srcWidth >> 1 ), mipHeight = Q_max( 1, srcHeight >> 1 );
-
-	for( int y = 0; y < mipHeight; y++, in += instride * 2 )
-	{
-		byte *next = ((( y << 1 ) + 1 ) < srcHeight ) ? ( in + instride ) : in;
-		for( int x = 0, row = 0; x < mipWidth; x++, row += 8, out += 4 )
-		{
-			if((( x << 1 ) + 1 ) < srcWidth )
-			{
-				for( int c = 0; c < 4; c++ )
-					out[c] = ( in[row + c] + in[row + 4 + c] + next[row + c] + next[row + 4 + c] ) >> 2;
-			}
-			else
-			{
-				for( int c = 0; c < 4; c++ )
-					out[c] = ( in[row + c] + next[row + c] ) >> 1;
-			}
-		}
-	}
+	return name && name[0] && strlen( name ) < sizeof( rc.images->name );
 }
 
-/* GL_UploadTexture (r_image.c:214-283): RGBA8 -> pixel_t for 4 mips, alpha plane, colour key.
- * Like the reference it filters the caller's RGBA buffer in place. */
-static qboolean rc_upload_image( rc_image_t *tex, rgbdata_t *pic )
+static int rc_image_index( const rc_image_t *tex ) { return tex ? (int)( tex - rc.images ) : 0; }
+
+/* tex takes a private copy of pic's pixels; false = format not supported */
+static qboolean rc_image_take( rc_image_t *tex, const rgbdata_t *pic )
 {
 	tex->srcWidth = tex->width = Q_max( 1, pic->width );
 	tex->srcHeight = tex->height = Q_max( 1, pic->height );
-	if( pic->flags & IMAGE_HAS_ALPHA )
-		tex->flags |= TF_HAS_ALPHA;
+	if( FBitSet( pic->flags, IMAGE_HAS_ALPHA ))
+		SetBits( tex->flags, TF_HAS_ALPHA );
 	if( !pic->buffer )
-		return true;
+		return true; /* a sized, empty texture */
 	if( pic->type != PF_RGBA_32 )
 	{
 		rc_error( "texture %s: unsupported pixel format %d", tex->name, pic->type );
 		return false;
 	}
-
-	byte *data = pic->buffer;
-	for( uint j = 0; j < 4; j++ )
-	{
-		uint width = Q_max( 1, ( tex->width >> j )), height = Q_max( 1, ( tex->height >> j ));
-
-		rc_free( tex->pixels[j] );
-		tex->pixels[j] = rc_malloc( width * height * sizeof( uint16_t ));
-		if( j == 0 && ( tex->flags & TF_HAS_ALPHA ))
-		{
-			rc_free( tex->alpha_pixels );
-			tex->alpha_pixels = rc_malloc( width * height * sizeof( uint16_t ));
-		}
-		for( uint i = 0; i < height * width; i++ )
-		{
-			uint r = data[i * 4 + 0] * 32 / 256, g = data[i * 4 + 1] * 64 / 256, b = data[i * 4 + 2] * 32 / 256;
-			tex->pixels[j][i] = rc_encode565( r, g, b );
-			if( j == 0 && tex->alpha_pixels )
-			{
-				uint alpha = ( data[i * 4 + 3] * 8 / 256 ) << ( 16 - 3 );
-				tex->alpha_pixels[i] = ( tex->pixels[j][i] >> 3 ) | alpha;
-				if( !sw_noalphabrushes.value && data[i * 4 + 3] < 128 && FBitSet( pic->flags, IMAGE_ONEBIT_ALPHA ))
-					tex->pixels[j][i] = RC_TRANSPARENT_COLOR;
-			}
-		}
-		rc_build_mipmap( data, width, height );
-	}
+	const size_t bytes = (size_t)tex->width * tex->height * 4;
+	rc_free( tex->rgba );
+	tex->rgba = rc_malloc( bytes );
+	memcpy( tex->rgba, pic->buffer, bytes );
+	tex->has_alpha = FBitSet( tex->flags, TF_HAS_ALPHA ) != 0;
+	tex->colorkey = tex->has_alpha && !sw_noalphabrushes.value && FBitSet( pic->flags, IMAGE_ONEBIT_ALPHA );
 	rc.textures_dirty = true;
 	return true;
 }
 
-static int GL_LoadTextureFromBuffer( const char *name, rgbdata_t *pic, texFlags_t flags, qboolean update )
+/* register (or, with update, refresh) the texture `name` from pic; 0 = failure, else its number */
+static int rc_texture_store( const char *name, const rgbdata_t *pic, uint flags, qboolean update )
 {
-	if( ( !name || !name[0] ) || strlen( name ) >= sizeof( rc.images->name ))
-		return 0;
-
 	rc_image_t *tex = rc_find_image( name );
 	if( tex && !update )
-		return tex - rc.images;
+		return rc_image_index( tex ); /* known already */
 	if( !pic )
 		return 0;
-	if( update )
-	{
-		if( !tex )
-			gEngfuncs.Host_Error( "%s: couldn't find texture %s for update\n", __func__, name );
-		SetBits( tex->flags, flags );
-	}
+	if( update && !tex )
+		gEngfuncs.Host_Error( "%s: couldn't find texture %s for update\n", __func__, name );
+	if( tex ) SetBits( tex->flags, flags );
 	else tex = rc_alloc_image( name, flags );
+	if( rc_image_take( tex, pic ))
+		return rc_image_index( tex );
+	rc_free( tex->rgba );
+	memset( tex, 0, sizeof( *tex ));
+	return 0;
+}
 
-	if( !rc_upload_image( tex, pic ))
-	{
-		memset( tex, 0, sizeof( *tex ));
-		return 0;
-	}
-	return tex - rc.images;
+static int GL_LoadTextureFromBuffer( const char *name, rgbdata_t *pic, texFlags_t flags, qboolean update )
+{
+	return rc_name_ok( name ) ? rc_texture_store( name, pic, flags, update ) : 0;
 }
 
 static int GL_LoadTexture( const char *name, const byte *buf, size_t size, int flags )
 {
-	if( ( !name || !name[0] ) || strlen( name ) >= sizeof( rc.images->name ))
+	if( !rc_name_ok( name ))
 		return 0;
-
-	rc_image_t *tex = rc_find_image( name );
-	if( tex )
-		return tex - rc.images;
-
-	uint picFlags = 0;
-	if( FBitSet( flags, TF_NOFLIP_TGA )) SetBits( picFlags, IL_DONTFLIP_TGA );
-	if( FBitSet( flags, TF_KEEP_SOURCE ) && !FBitSet( flags, TF_EXPAND_SOURCE )) SetBits( picFlags, IL_KEEP_8BIT );
-	gEngfuncs.Image_SetForceFlags( picFlags );
-
+	const int known = rc_image_index( rc_find_image( name ));
+	if( known )
+		return known;
+	/* the engine's image loader decodes the file; these two switches are what the reference asks of it (r_image.c:508-514) */
+	const uint force = ( FBitSet( flags, TF_NOFLIP_TGA ) ? IL_DONTFLIP_TGA : 0 )
+		| (( FBitSet( flags, TF_KEEP_SOURCE ) && !FBitSet( flags, TF_EXPAND_SOURCE )) ? IL_KEEP_8BIT : 0 );
+	gEngfuncs.Image_SetForceFlags( force );
 	rgbdata_t *pic = gEngfuncs.FS_LoadImage( name, buf, size );
 	if( !pic )
 		return 0;
-
-	tex = rc_alloc_image( name, flags );
-	if( !rc_upload_image( tex, pic ))
-	{
-		memset( tex, 0, sizeof( *tex ));
-		gEngfuncs.FS_FreeImage( pic );
-		return 0;
-	}
+	const int texnum = rc_texture_store( name, pic, flags, false );
 	gEngfuncs.FS_FreeImage( pic );
-	return tex - rc.images;
+	return texnum;
 }
 
 static int GL_CreateTexture( const char *name, int width, int height, const void *buffer, texFlags_t flags )
 {
-	rgbdata_t r_empty;
-	memset( &r_empty, 0, sizeof( r_empty ));
-	r_empty.width = width;
-	r_empty.height = height;
-	r_empty.type = PF_RGBA_32;
-	r_empty.size = width * height * 4;
-	r_empty.flags = IMAGE_HAS_COLOR | ( FBitSet( flags, TF_HAS_ALPHA ) ? IMAGE_HAS_ALPHA : 0 );
 	if( FBitSet( flags, TF_CUBEMAP ))
 		return 0;
-
-	/* the upload filters its source in place (as the reference does): work on a copy of caller memory */
-	byte *copy = NULL;
-	if( buffer )
-	{
-		copy = rc_malloc( r_empty.size );
-		memcpy( copy, buffer, r_empty.size );
-	}
-	r_empty.buffer = copy;
-	int texnum = GL_LoadTextureFromBuffer( name, &r_empty, flags, false );
-	rc_free( copy );
-	return texnum;
+	rgbdata_t pic;
+	memset( &pic, 0, sizeof( pic ));
+	pic.width = width; pic.height = height;
+	pic.type = PF_RGBA_32;
+	pic.size = width * height * 4;
+	pic.flags = IMAGE_HAS_COLOR | ( FBitSet( flags, TF_HAS_ALPHA ) ? IMAGE_HAS_ALPHA : 0 );
+	pic.buffer = (byte *)buffer; /* only read: the texture keeps a copy */
+	return GL_LoadTextureFromBuffer( name, &pic, flags, false );
 }
 
 static int GL_FindTexture( const char *name )
@@ -405,50 +348,50 @@ static void GL_FreeTexture( unsigned int texnum )
 	rc_delete_image( &rc.images[texnum] );
 }
 
-/* pack every live texture into one pixel_t arena and hand it to the device */
+/* lay out the pixel_t arena (four mips + alpha plane per live texture), gather the RGBA sources in one upload arena and let
+ * the device encode them */
 static void rc_sync_textures( void )
 {
 	if( !rc.textures_dirty )
 		return;
-
-	size_t total = 0;
-	for( int i = 0; i < rc.numImages; i++ )
-	{
-		rc_image_t *t = &rc.images[i];
-		if( !t->pixels[0] ) continue;
-		for( int j = 0; j < 4; j++ )
-			total += (size_t)Q_max( 1, t->width >> j ) * Q_max( 1, t->height >> j );
-		if( t->alpha_pixels ) total += (size_t)t->width * t->height;
-	}
+	const int n = rc.numImages;
 	rc_free( rc.textab );
-	rc_texture_t *tab = rc.textab = rc_malloc( sizeof( rc_texture_t ) * Q_max( 1, rc.numImages ));
-	rc.ntextab = rc.numImages;
-	uint16_t *arena = rc_malloc(( total + 64 ) * sizeof( uint16_t ));
-	size_t o = 0;
-	for( int i = 0; i < rc.numImages; i++ )
+	rc_texture_t *tab = rc.textab = rc_malloc( sizeof( rc_texture_t ) * Q_max( 1, n ));
+	rc_texsrc_t *src = rc_malloc( sizeof( rc_texsrc_t ) * Q_max( 1, n ));
+	rc.ntextab = n;
+	size_t ntexels = 0, nrgba = 0;
+	for( int i = 0; i < n; i++ )
 	{
-		rc_image_t *t = &rc.images[i];
+		const rc_image_t *t = &rc.images[i];
 		rc_texture_t *d = &tab[i];
 		d->width = t->width; d->height = t->height; d->flags = t->flags; d->alpha_ofs = -1;
-		for( int j = 0; j < 4; j++ ) d->ofs[j] = 0;
-		if( !t->pixels[0] ) continue;
+		for( int j = 0; j < 4; j++ ) d->ofs[j] = RC_IMAGE_LIVE( t ) ? 0 : -1;
+		if( !RC_IMAGE_LIVE( t ))
+			continue;
 		for( int j = 0; j < 4; j++ )
 		{
-			size_t n = (size_t)Q_max( 1, t->width >> j ) * Q_max( 1, t->height >> j );
-			d->ofs[j] = (int32_t)o;
-			memcpy( arena + o, t->pixels[j], n * sizeof( uint16_t ));
-			o += n;
+			d->ofs[j] = (int32_t)ntexels;
+			ntexels += (size_t)Q_max( 1, t->width >> j ) * Q_max( 1, t->height >> j );
 		}
-		if( t->alpha_pixels )
+		if( t->has_alpha )
 		{
-			size_t n = (size_t)t->width * t->height;
-			d->alpha_ofs = (int32_t)o;
-			memcpy( arena + o, t->alpha_pixels, n * sizeof( uint16_t ));
-			o += n;
+			d->alpha_ofs = (int32_t)ntexels;
+			ntexels += (size_t)t->width * t->height;
 		}
+		src[i].rgba_ofs = (uint32_t)nrgba;
+		src[i].flags = t->colorkey ? RC_TEXSRC_COLORKEY : 0;
+		nrgba += (size_t)t->width * t->height;
 	}
-	RC_CHECK_DEV( rc_dev_upload_textures( tab, rc.numImages, arena, total + 64 ));
-	rc_free( arena );
+	uint32_t *arena = rc_malloc(( nrgba + 1 ) * sizeof( uint32_t ));
+	for( int i = 0; i < n; i++ )
+		if( RC_IMAGE_LIVE( &rc.images[i] ))
+			memcpy( arena + src[i].rgba_ofs, rc.images[i].rgba, (size_t)rc.images[i].width * rc.images[i].height * 4 );
+	RC_CHECK_DEV( rc_dev_upload_textures( tab, src, n, arena, nrgba, ntexels + 64 ));
+	rc_free( arena ); rc_free( src );
+	/* textures without an image keep offset 0 in the table the other host code reads (rc_texture_entry checks liveness) */
+	for( int i = 0; i < n; i++ )
+		if( !RC_IMAGE_LIVE( &rc.images[i] ))
+			for( int j = 0; j < 4; j++ ) tab[i].ofs[j] = 0;
 	rc.textures_dirty = false;
 }
 
@@ -471,37 +414,35 @@ static int rc_tree_depth( const model_t *mod, const mnode_t *n, int d )
 	return a > b ? a : b;
 }
 
-/* R_TextureAnimation (ref/soft/r_surf.c:239-284) for the world entity (curstate.frame == 0) */
-static uint16_t rc_rtable[MOD_FRAMES][MOD_FRAMES];
+/* the random numbers "-" (random-tiled) textures choose their tile with, drawn at R_Init (GL_InitRandomTable,
+ * ref/common/ref_context.c:46) */
+static uint16_t rc_tile_random[MOD_FRAMES][MOD_FRAMES];
 
-static int rc_texture_animation( const msurface_t *s )
+/* which texture a world face shows at the client's time (what R_TextureAnimation, ref/soft/r_surf.c:239, answers for the
+ * world entity): the frame of the "+0".."+9" chain whose [anim_min, anim_max) window holds the wanted tick; a "-" texture
+ * wants the tile its position in texture space draws from the random table */
+static int rc_surface_texture( const msurface_t *s )
 {
-	texture_t *base = s->texinfo->texture;
-	int reletive;
-
-	if( !base->anim_total )
-		return base->gl_texturenum;
-
-	if( base->name[0] == '-' )
+	texture_t *first = s->texinfo->texture;
+	if( !first->anim_total )
+		return first->gl_texturenum;
+	int want;
+	if( first->name[0] == '-' )
 	{
-		int tx = (int)(( s->texturemins[0] + ( base->width << 16 )) / base->width ) % MOD_FRAMES;
-		int ty = (int)(( s->texturemins[1] + ( base->height << 16 )) / base->height ) % MOD_FRAMES;
-		reletive = rc_rtable[tx][ty] % base->anim_total;
+		const int col = (int)(( s->texturemins[0] + ( first->width << 16 )) / first->width ) % MOD_FRAMES;
+		const int row = (int)(( s->texturemins[1] + ( first->height << 16 )) / first->height ) % MOD_FRAMES;
+		want = rc_tile_random[col][row] % first->anim_total;
 	}
 	else
 	{
-		int speed = FBitSet( rc.images[base->gl_texturenum].flags, TF_QUAKEPAL ) ? 10 : 20;
-		reletive = (int)( gp_cl->time * speed ) % base->anim_total;
+		const int ticks_per_second = FBitSet( rc.images[first->gl_texturenum].flags, TF_QUAKEPAL ) ? 10 : 20;
+		want = (int)( gp_cl->time * ticks_per_second ) % first->anim_total;
 	}
-
-	int count = 0;
-	while( base->anim_min > reletive || base->anim_max <= reletive )
-	{
-		base = base->anim_next;
-		if( !base || ++count > MOD_FRAMES )
-			return s->texinfo->texture->gl_texturenum;
-	}
-	return base->gl_texturenum;
+	int hops = 0;
+	for( texture_t *t = first; t && hops <= MOD_FRAMES; t = t->anim_next, hops++ )
+		if( want >= t->anim_min && want < t->anim_max )
+			return t->gl_texturenum;
+	return first->gl_texturenum; /* broken chain */
 }
 
 static void rc_resolve_texnums( qboolean force )
@@ -510,7 +451,7 @@ static void rc_resolve_texnums( qboolean force )
 	qboolean changed = force;
 	for( int i = 0; i < w->numsurfaces; i++ )
 	{
-		int t = rc_texture_animation( &w->surfaces[i] );
+		int t = rc_surface_texture( &w->surfaces[i] );
 		if( t != rc.surf_texnum[i] ) { rc.surf_texnum[i] = t; changed = true; }
 	}
 	if( changed && !force )
@@ -617,7 +558,7 @@ static void R_NewMap( void )
 		d->flags = s->flags;
 		d->firstedge = s->firstedge;
 		d->numedges = s->numedges;
-		d->texnum = rc.surf_texnum[i] = rc_texture_animation( s );
+		d->texnum = rc.surf_texnum[i] = rc_surface_texture( s );
 		d->sample_size = gEngfuncs.Mod_SampleSizeForFace( s );
 		d->texflags = s->texinfo->flags;
 		for( int j = 0; j < 4; j++ ) d->styles[j] = s->styles[j];
@@ -679,52 +620,39 @@ static void R_NewMap( void )
 /* ---------------------------------------------------------------------------------------------- */
 /* light styles: CL_RunLightStyles, ref/common/ref_light.c:30-87                                   */
 
+/* the brightness (x 256) a style shows at its own clock: the letter under the clock's tenth of a second, 'a' = 0 .. 'z' = 25
+ * in steps of 22; interpolated styles blend it with the next letter (float, truncated as the reference does) */
+static int rc_lightstyle_value( const lightstyle_t *st, qboolean blend )
+{
+	if( !st->length )
+		return 256; /* no pattern: normal light */
+	if( st->length == 1 )
+		return st->map[0] * 22;
+	const int tick = (int)Q_floor( st->time * 10 );
+	if( !( blend && st->interp ))
+		return st->map[tick % st->length] * 22;
+	const int next = (int)Q_ceil( st->time * 10 );
+	const float towards_next = ( st->time * 10 ) - tick, towards_this = 1.0f - towards_next;
+	float value = (float)( st->map[tick % st->length] * 22.0f ) * towards_this;
+	value += (float)( st->map[next % st->length] * 22.0f ) * towards_next;
+	return (int)value;
+}
+
+/* the CL_RunLightStyles slot (ref/common/ref_light.c:30): advance every style's clock by the frame time, then sample all 256 */
 static void CL_RunLightStyles( lightstyle_t *ls )
 {
 	const model_t *world = gp_cl->models[1];
-	float frametime = gp_cl->time - gp_cl->oldtime;
-
 	if( !world )
 		return;
-
-	if( r_fullbright->value || !world->lightdata )
-	{
-		for( int i = 0; i < MAX_LIGHTSTYLES; i++ )
-			rc.lightstylevalue[i] = 256 * 256;
-		return;
-	}
-
+	const qboolean everything_lit = r_fullbright->value || !world->lightdata;
+	const float dt = gp_cl->time - gp_cl->oldtime;
+	const qboolean clocks_run = !everything_lit && !gp_cl->paused && dt <= 0.1f;
+	const qboolean blend = cl_lightstyle_lerping->value != 0;
 	for( int i = 0; i < MAX_LIGHTSTYLES; i++ )
 	{
-		if( !gp_cl->paused && frametime <= 0.1f )
-			ls[i].time += frametime;
-
-		if( !ls[i].length )
-		{
-			rc.lightstylevalue[i] = 256;
-			continue;
-		}
-		if( ls[i].length == 1 )
-		{
-			rc.lightstylevalue[i] = ls[i].map[0] * 22;
-			continue;
-		}
-
-		int flight = (int)Q_floor( ls[i].time * 10 );
-		if( !ls[i].interp || !cl_lightstyle_lerping->value )
-		{
-			rc.lightstylevalue[i] = ls[i].map[flight % ls[i].length] * 22;
-			continue;
-		}
-
-		int clight = (int)Q_ceil( ls[i].time * 10 );
-		float lerpfrac = ( ls[i].time * 10 ) - flight;
-		float backlerp = 1.0f - lerpfrac;
-		int k = ls[i].map[flight % ls[i].length];
-		float l = (float)( k * 22.0f ) * backlerp;
-		k = ls[i].map[clight % ls[i].length];
-		l += (float)( k * 22.0f ) * lerpfrac;
-		rc.lightstylevalue[i] = (int)l;
+		if( clocks_run )
+			ls[i].time += dt;
+		rc.lightstylevalue[i] = everything_lit ? 256 * 256 : rc_lightstyle_value( &ls[i], blend );
 	}
 }
 
@@ -872,7 +800,7 @@ static void rc_push_dlights( void )
 
 static const rc_texture_t *rc_texture_entry( int texnum )
 {
-	return ( texnum > 0 && texnum < rc.ntextab && rc.images[texnum].pixels[0] ) ? &rc.textab[texnum] : NULL;
+	return ( texnum > 0 && texnum < rc.ntextab && RC_IMAGE_LIVE( &rc.images[texnum] )) ? &rc.textab[texnum] : NULL;
 }
 
 /* ---------------------------------------------------------------------------------------------- */
@@ -1054,7 +982,7 @@ static void GL_Bind( int tmu, unsigned int texnum )
 	const rc_image_t *image = &rc.images[texnum];
 	const int mode = rc.tri.rendermode;
 	rc.tri.drawer = mode == kRenderNormal ? RC_DRAW_FILL : mode == kRenderTransAdd ? RC_DRAW_ADDITIVE : mode == kRenderGlow ? RC_DRAW_GLOW
-		: image->alpha_pixels ? RC_DRAW_TEXBLEND : RC_DRAW_BLEND;
+		: image->has_alpha ? RC_DRAW_TEXBLEND : RC_DRAW_BLEND;
 	rc.tri.texnum = (int)texnum;
 	rc.tri.skinwidth = image->width; rc.tri.skinheight = image->height;
 }
@@ -2273,7 +2201,7 @@ static qboolean R_Init( void )
 	/* GL_InitRandomTable, ref/common/ref_context.c:46-56 */
 	for( int tu = 0; tu < MOD_FRAMES; tu++ )
 		for( int tv = 0; tv < MOD_FRAMES; tv++ )
-			rc_rtable[tu][tv] = gEngfuncs.COM_RandomLong( 0, 0x7FFF );
+			rc_tile_random[tu][tv] = gEngfuncs.COM_RandomLong( 0, 0x7FFF );
 	gEngfuncs.COM_SetRandomSeed( 0 );
 
 	for( int i = 0; i < MAX_LIGHTSTYLES; i++ ) rc.lightstylevalue[i] = 256;
@@ -2355,7 +2283,7 @@ static void R_DrawStretchPic( float fx, float fy, float fw, float fh, float fs1,
 	if( x < 0 ) { s1 += ( -x ) * ( s2 - s1 ) / w; x = 0; }
 	if( x + w > vw ) { s2 -= ( x + w - vw ) * ( s2 - s1 ) / w; w = vw - x; }
 	if( y + h > vh ) { t2 -= ( y + h - vh ) * ( t2 - t1 ) / h; h = vh - y; }
-	if( !pic->pixels[0] || s1 >= s2 || t1 >= t2 )
+	if( !RC_IMAGE_LIVE( pic ) || s1 >= s2 || t1 >= t2 )
 		return;
 	unsigned int height = h;
 	int skip = 0;
@@ -2368,7 +2296,7 @@ static void R_DrawStretchPic( float fx, float fy, float fw, float fh, float fs1,
 	c->kind = RC_2D_PIC; c->x = x; c->y = y; c->w = w; c->h = h; c->s1 = s1; c->t1 = t1; c->s2 = s2; c->t2 = t2;
 	c->skip = skip; c->height = (int)height;
 	c->tex_ofs = texnum; /* resolved to an arena offset when the pass is sent */
-	c->texwidth = pic->width; c->transparent = pic->alpha_pixels != NULL;
+	c->texwidth = pic->width; c->transparent = pic->has_alpha;
 }
 
 /* CL_FillRGBA + Draw_Fill (ref/soft/r_context.c:44, r_draw.c:159) */
@@ -2539,7 +2467,7 @@ static intptr_t RefGetParm( int parm, int arg )
 	case PARM_TEX_HEIGHT: return t->height;
 	case PARM_TEX_SRC_WIDTH: return t->srcWidth;
 	case PARM_TEX_SRC_HEIGHT: return t->srcHeight;
-	case PARM_TEX_MIPCOUNT: return t->pixels[0] ? 4 : 0;
+	case PARM_TEX_MIPCOUNT: return RC_IMAGE_LIVE( t ) ? 4 : 0;
 	case PARM_TEX_DEPTH: return 1;
 	case PARM_TEX_FLAGS: return t->flags;
 	case PARM_LIGHTSTYLEVALUE: return rc.lightstylevalue[bound( 0, arg, MAX_LIGHTSTYLES - 1 )];

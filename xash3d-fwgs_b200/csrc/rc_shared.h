@@ -83,6 +83,14 @@ typedef struct
 	int32_t flags;
 } rc_texture_t; /* 32 B */
 
+/* source of a texture for the device-side encode (k_tex_encode): its RGBA8 image in the batch's source arena */
+#define RC_TEXSRC_COLORKEY 1 /* IMAGE_ONEBIT_ALPHA and sw_noalphabrushes off: alpha < 128 becomes TRANSPARENT_COLOR at mip 0 */
+typedef struct
+{
+	uint32_t rgba_ofs;  /* first texel (uint32 RGBA, byte order R G B A) in the source arena */
+	int32_t  flags;     /* RC_TEXSRC_* */
+} rc_texsrc_t;
+
 /* static world, device pointers (filled by rc_dev_upload_scene) */
 typedef struct
 {

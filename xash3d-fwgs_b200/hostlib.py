@@ -1,4 +1,4 @@
-"""ctypes binding of libxashhost.so, the headless engine stand-in (csrc/host/xh_host.h).
+"""ctypes binding of libxashhost.so, the headless engine stand-in (harness/xh_host.h at the repository root: test and bench infrastructure).
 
 One `Host` == one engine instance == one private copy of the library image (the renderer ABI has
 no context pointer and renderers keep process-global state), so two renderers - e.g. the oracle
@@ -15,7 +15,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_HERE)
-HOST_LIB_PATH = os.path.join(_HERE, "libxashhost.so")
+HOST_LIB_PATH = os.path.join(os.path.dirname(_HERE), "harness", "libxashhost.so")
 REF_CUDA_PATH = os.path.join(_HERE, "libref_cuda.so")
 REF_SOFT_PATH = os.path.join(_ROOT, "oracle", "_ref", "libref_soft.so")
 
