@@ -20,6 +20,9 @@ and the counters).
 from __future__ import annotations
 
 import argparse
+import os as _os
+
+_os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")  # before torch creates the CUDA context: see rc_dev_init (rc_device.cu)
 import importlib
 import json
 import os
@@ -380,23 +383,40 @@ def run_cuda(args):
     ms_blit = allmax(float(np.median(blit_ms[max(args.warmup, 3):])))
 
     # -- e2e: the public C-ABI call with host buffers (H2D view descriptors, D2H colour frames), wall clock
-    def e2e_leg(zptr):
+    def e2e_leg(zptr, pipelined):
+        """the public batch call with host buffers.  pipelined: RefCuda_RenderViewsAsync with two alternating sets of pinned
+        buffers and RefCuda_Wait before a set is handed out again (every step's frames are complete in host memory one step
+        later); else the blocking RefCuda_RenderViews."""
+        outs = [(pin.data_ptr(), zptr), (pin_b.data_ptr(), zptr_b if zptr else None)]
+
+        def step(k):
+            advance(args, r, k)
+            if pipelined:
+                r.render_prepared_async(vp, *outs[k & 1])
+            else:
+                r.render_prepared(vp, pin.data_ptr(), zptr)
+
         for k in range(max(args.warmup, 3)):
-            advance(args, r, k + 1)
-            r.render_prepared(vp, pin.data_ptr(), zptr)
+            step(k + 1)
+        r.wait()
         barrier()
         t0 = time.perf_counter()
         for k in range(args.steps):
-            advance(args, r, k + 100)
-            r.render_prepared(vp, pin.data_ptr(), zptr)
+            step(k + 100)
+        r.wait()
         torch.cuda.synchronize()
         secs = allmax((time.perf_counter() - t0) / args.steps)
         barrier()
         return secs
 
-    e2e_s = e2e_leg(None)
+    pin_b = torch.empty((n, h, w), dtype=torch.int16).pin_memory()
+    zptr_b = torch.empty((n, h, w), dtype=torch.int16).pin_memory()
+    zptr_b_keep = zptr_b
+    zptr_b = zptr_b.data_ptr()
+    e2e_sync_s = e2e_leg(None, False)
+    e2e_s = e2e_leg(None, True)
     h2d = r.batch_h2d_bytes()
-    e2e_z_s = e2e_leg(pin_z.data_ptr())
+    e2e_z_s = e2e_leg(pin_z.data_ptr(), True)
     clocks = sampler.stop() if sampler else None
 
     # counters of the last batch, summed over ranks (the only collective: < 1 KiB, off the data path)
@@ -419,7 +439,9 @@ def run_cuda(args):
                          "note": "the surface-cache kernels run on a side stream beside span generation: their time overlaps spans and is not part of the sum"},
             "e2e": {"value": total_px / e2e_s / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": px * 2 + 512,
                     "ms_per_step": e2e_s * 1e3,
-                    "note": "RefCuda_RenderViews, host buffers: per-view constants (+ light styles when they change) host->device, colour frames "
+                    "blocking_call_ms_per_step": e2e_sync_s * 1e3, "blocking_call_value": total_px / e2e_sync_s / 1e6,
+                    "note": "RefCuda_RenderViewsAsync + RefCuda_Wait, two alternating sets of pinned host buffers (batch k's copies run under batch k+1's stages; "
+                            "blocking_call_* = the same batch through the blocking RefCuda_RenderViews): per-view constants (+ light styles when they change) host->device, colour frames "
                             "(what an observation consumer takes) device->host into pinned memory, 512 B of counters"},
             "e2e_colour_and_z": {"value": total_px / e2e_z_s / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": px * 4 + 512,
                                  "ms_per_step": e2e_z_s * 1e3, "note": "the same call with the z buffers copied out as well (what the reference arm leaves in host memory)"},

@@ -40,6 +40,17 @@ REF_CUDA_EXPORT int GetRefAPI( int version, struct ref_interface_s *pFunctionTab
 REF_CUDA_EXPORT int RefCuda_RenderViews( const struct ref_viewpass_s *views, int nviews, unsigned short *color_out, short *z_out, int clear );
 
 /*
+ * The same batch, enqueued only: returns once the work is queued; color_out / z_out (pinned host memory, or the copies
+ * degrade to synchronous ones) are complete after RefCuda_Wait.  A harness that renders batch after batch calls
+ * RefCuda_RenderViewsAsync with alternating output buffers and RefCuda_Wait before it reads one: successive asynchronous
+ * batches draw into alternating sets of device frame buffers, so the device->host copies of batch k (PCIe: the long pole of
+ * the synchronous call) run under the stages of batch k + 1.  Every other RefCuda_* / ref_interface_t call waits first.
+ * Batches with clear == 0, without host outputs or with fewer than 64 views run synchronously.
+ */
+REF_CUDA_EXPORT int RefCuda_RenderViewsAsync( const struct ref_viewpass_s *views, int nviews, unsigned short *color_out, short *z_out, int clear );
+REF_CUDA_EXPORT int RefCuda_Wait( void );
+
+/*
  * Display tail on the device (R_BuildScreenMap + R_BlitScreen, ref/soft/r_glblit.c:347-407,591-721): converts views
  * [first, first + nviews) of the last RefCuda_RenderViews batch, which stay in HBM, from pixel_t to a display format
  * described the way SW_CreateBuffer (engine/ref_api.h) describes the engine's surface - bpp 2 or 4 bytes and the three

@@ -413,6 +413,7 @@ static void emu_draw_items( const rc_view_t *vw, const emu_viewctx_t &cx, uint16
 	if( K_active ) emu_keys_resolve( color, zb, width, height );
 }
 
+int rc_dev_wait( void ) { return 0; }
 int rc_dev_set_lightstyles( const int32_t *values ) { memcpy( E.styles, values, sizeof( E.styles )); return 0; }
 int rc_dev_flush_cache( void ) { for( auto &k : E.cachekey ) k.valid = false; return 0; }
 
@@ -612,6 +613,11 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 		E.counters[RC_CTR_VIEWS]++; E.counters[RC_CTR_PIXELS] += (uint64_t)vw_w * vw_h;
 	}
 	return 0;
+}
+
+int rc_dev_render_async( const rc_view_t *views, int nviews, int width, int height, int clear, uint16_t *color_out, int16_t *z_out )
+{
+	return rc_dev_render( views, nviews, width, height, clear, color_out, z_out ); /* nothing is asynchronous here */
 }
 
 /* dynamic lights are not part of the debug harness */

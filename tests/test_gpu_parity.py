@@ -625,3 +625,28 @@ def test_translucent_brush_entities_match_oracle(pkg, scene):
     cc, cz = cu.render_views(m.cameras[:32])
     rc, rz = so.render_views(m.cameras[:32])
     assert np.array_equal(cc, rc) and np.array_equal(cz, rz), ((cc == rc).mean(), (cz == rz).mean())
+
+
+def test_async_batches_match_synchronous_ones(pkg, scene):
+    """RefCuda_RenderViewsAsync / RefCuda_Wait: batches enqueued back to back with alternating host buffers (the copies of
+    one run under the stages of the next, two sets of device frame buffers) deliver what the synchronous call delivers,
+    also when a synchronous call follows an asynchronous one."""
+    import ctypes as C
+    m = scene.make_map("small", ncameras=256)
+    cu = scene.Renderer(pkg.REF_CUDA_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    sets = [m.cameras[0:96], m.cameras[96:192], m.cameras[160:256], m.cameras[32:128]]
+    want = [so.render_views(c) for c in sets]
+    bufs = [(np.zeros((96, 240, 320), np.uint16), np.zeros((96, 240, 320), np.int16)) for _ in sets]
+    for c, (col, z) in zip(sets, bufs):  # nothing is waited for in between
+        cu.render_prepared_async(cu.viewpasses(c), col.ctypes.data, z.ctypes.data)
+    cu.wait()
+    for (col, z), (rc, rz) in zip(bufs, want):
+        assert np.array_equal(col, rc) and np.array_equal(z, rz)
+    # a synchronous call right after an asynchronous one
+    col, z = bufs[0]
+    col[:] = 0
+    cu.render_prepared_async(cu.viewpasses(sets[1]), col.ctypes.data, z.ctypes.data)
+    cc, cz = cu.render_views(sets[2])
+    assert np.array_equal(col, want[1][0]) and np.array_equal(cc, want[2][0]) and np.array_equal(cz, want[2][1])
+    assert all(v == 0 for k, v in cu.counters().items() if k.startswith("overflow"))

@@ -56,6 +56,10 @@ int rc_dev_flush_cache( void );
  * clear: non-zero -> framebuffers start as zeros (the reference never clears; harnesses zero both sides).
  */
 int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, int clear, uint16_t *color_out, int16_t *z_out );
+/* the same, enqueued only: the outputs are complete after rc_dev_wait.  Successive asynchronous batches alternate between two
+ * sets of frame buffers, so that the device->host copies of one batch run under the stages of the next */
+int rc_dev_render_async( const rc_view_t *views, int nviews, int width, int height, int clear, uint16_t *color_out, int16_t *z_out );
+int rc_dev_wait( void );
 
 /* re-run the device stages of the last rc_dev_render batch (inputs resident in HBM) 'iters' times and
  * report CUDA-event milliseconds: total and per stage (vis+walk, faces, cache, spans, draw, entities).  The cache kernels run

@@ -21,6 +21,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <time.h>
 
 #include <vector>
 
@@ -638,6 +639,32 @@ __global__ void __launch_bounds__( 256 ) k_blit( const uint16_t *__restrict__ co
 		}
 }
 
+/* fills of the batch path as kernels: a cudaMemsetAsync may be served by a copy engine, where it would queue behind the
+ * frames another batch is copying to the host (measured: every stage of an asynchronous batch started 0.7 ms late) */
+__global__ void k_fill32( uint32_t *dst, uint32_t value, size_t n )
+{
+	for( size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x ) dst[i] = value;
+}
+__global__ void k_copy32( uint32_t *dst, const uint32_t *src, size_t n )
+{
+	for( size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x ) dst[i] = src[i];
+}
+static inline void fill32( void *dst, uint32_t value, size_t nwords, cudaStream_t st )
+{
+	if( !nwords ) return;
+	size_t blocks = ( nwords + 255 ) / 256;
+	if( blocks > 148 * 8 ) blocks = 148 * 8;
+	k_fill32<<<(unsigned)blocks, 256, 0, st>>>( (uint32_t *)dst, value, nwords );
+}
+
+/* the batch counters into their mapped pinned mirror: a store over PCIe instead of a copy that would queue behind the frames
+ * on the device->host copy engine (the host reads the mirror once the batch's kernels are done, before its copies are) */
+__global__ void k_counters_out( const unsigned long long *src, unsigned long long *dst )
+{
+	dst[threadIdx.x] = src[threadIdx.x];
+	__threadfence_system();
+}
+
 struct Dev
 {
 	bool ready = false;
@@ -676,11 +703,24 @@ struct Dev
 	/* batch work buffers (grown on demand) */
 	rc_work_t w{};
 	int cap_views = 0, cap_w = 0, cap_h = 0;
+	/* asynchronous batches (rc_dev_render_async): a second set of frame buffers, so that batch k's frames can be copied out
+	 * while batch k + 1 is drawn into the other set; the batch whose kernels have not been checked for overflows yet */
+	uint16_t *main_color = nullptr, *alt_color = nullptr; int16_t *main_zbuf = nullptr, *alt_zbuf = nullptr; size_t alt_px = 0; bool use_alt = false;
+	cudaEvent_t ev_kdone = nullptr; bool pending = false;
+	struct batch_graph_t { cudaGraphExec_t exec = nullptr; unsigned long long key = 0, launches = 0; };
+	batch_graph_t graphs[4][2]; /* [segment][frame buffer set] */
+	bool use_graphs = true;
+	cudaEvent_t ev_join[2] = {};
+	std::vector<rc_view_t> pend_views; int pend_w = 0, pend_h = 0, pend_clear = 0; uint16_t *pend_color = nullptr; int16_t *pend_z = nullptr;
 	/* per-view capacities: they start from what a view typically needs and follow the counters of the batches
 	 * rendered so far (a batch that overflows one is re-run with a larger one), never the worst case of the map */
 	int cap_cands = 0, cap_edges = 0, cap_blk_events = 0;
 	bool caps_dirty = false;
 	int vw_grid = 0;                         /* k_viswalk: resident blocks, persistent over views */
+	/* the per-view constants reach the device through mapped pinned staging read by a kernel (two buffers, alternating), not
+	 * through a copy engine: a host->device copy was seen to wait for the frames of the batch before */
+	rc_view_t *h_views[2] = { nullptr, nullptr }; size_t cap_hviews = 0; int hviews_turn = 0;
+	unsigned long long *h_counters_dev = nullptr; /* the mirror as the device sees it (mapped pinned memory) */
 	unsigned long long *h_counters = nullptr; /* pinned mirror of the batch counters, copied at the end of every batch */
 	rc_view_t *d_views = nullptr;
 	void *d_work[24] = {};
@@ -843,6 +883,10 @@ int ensure_batch( int nviews, int width, int height )
 	CK( cudaMemset( w.zbuf, 0, (size_t)cap * width * height * 2 ));
 	w.views = D.d_views;
 	D.cap_views = cap; D.cap_w = width; D.cap_h = height;
+	D.main_color = w.color; D.main_zbuf = w.zbuf; D.use_alt = false;
+	if( D.alt_color ) { cudaFree( D.alt_color ); D.alt_color = nullptr; }
+	if( D.alt_zbuf ) { cudaFree( D.alt_zbuf ); D.alt_zbuf = nullptr; }
+	D.alt_px = 0;
 	return 0;
 }
 
@@ -961,10 +1005,10 @@ int launch_studio_points( cudaStream_t st )
 int launch_slice( const rc_work_t &ws, int k, cudaStream_t st, cudaEvent_t *evs, bool draw )
 {
 	const rc_scene_t &sc = D.sc;
-	CK( cudaMemsetAsync( ws.cache_need, 0, sizeof( uint32_t ) * (( sc.numsurfaces * 4 + 31 ) / 32 + 1 ), st ));
-	CK( cudaMemsetAsync( ws.cache_nlist, 0, sizeof( int32_t ) * 16, st ));
-	if( D.nbents ) CK( cudaMemsetAsync( ws.viewbm, 0, sizeof( int32_t ) * (size_t)ws.nviews, st ));
-	if( D.nbents ) CK( cudaMemsetAsync( ws.leafbase, 0xFF, sizeof( int32_t ) * (size_t)ws.nviews * sc.numleafs, st ));
+	fill32( ws.cache_need, 0u, (size_t)(( sc.numsurfaces * 4 + 31 ) / 32 + 1 ), st );
+	fill32( ws.cache_nlist, 0u, 16, st );
+	if( D.nbents ) fill32( ws.viewbm, 0u, (size_t)ws.nviews, st );
+	if( D.nbents ) fill32( ws.leafbase, 0xFFFFFFFFu, (size_t)ws.nviews * sc.numleafs, st );
 	if( evs ) CK( cudaEventRecord( evs[0], st ));
 	k_viswalk<VW_NTHREADS><<<ws.nviews < D.vw_grid ? ws.nviews : D.vw_grid, VW_NTHREADS, (size_t)ws.vis_smem, st>>>( sc, ws );
 	D.launches++;
@@ -993,7 +1037,7 @@ int launch_slice( const rc_work_t &ws, int k, cudaStream_t st, cudaEvent_t *evs,
 	if( evs ) CK( cudaEventRecord( evs[2], st ));
 	{
 		/* the surface cache is only read by k_draw: its kernels run on a side stream, beside span generation */
-		cudaStream_t aux = D.cache_aside ? D.aux_stream[k] : st;
+		cudaStream_t aux = D.cache_aside ? D.aux_stream[k & 1] : st; /* as many side streams as slice streams: every stream costs a hardware queue */
 		CK( cudaEventRecord( D.ev_cache[k][0], st ));
 		if( D.cache_aside ) CK( cudaStreamWaitEvent( aux, D.ev_cache[k][0], 0 ));
 		int nslots = sc.numsurfaces * 4;
@@ -1061,6 +1105,33 @@ int launch_slice( const rc_work_t &ws, int k, cudaStream_t st, cudaEvent_t *evs,
 	return 0;
 }
 
+/* the stages of slices [k0, k0 + kn) of a batch, forked from st onto the slice streams and joined back into it */
+int enqueue_segment( const rc_work_t *wss, int k0, int kn, cudaStream_t st )
+{
+	CK( cudaEventRecord( D.ev_fork, st ));
+	for( int j = 0; j < kn; j++ )
+	{
+		cudaStream_t ss = D.slice_stream[j];
+		CK( cudaStreamWaitEvent( ss, D.ev_fork, 0 ));
+		if( launch_slice( wss[j], k0 + j, ss, nullptr, true ) != 0 ) return -1;
+		CK( cudaEventRecord( D.ev_join[j], ss ));
+	}
+	for( int j = 0; j < kn; j++ ) CK( cudaStreamWaitEvent( st, D.ev_join[j], 0 ));
+	return 0;
+}
+
+/* everything the launches of a segment are made from */
+unsigned long long segment_key( const rc_work_t *wss, int kn )
+{
+	unsigned long long h = 1469598103934665603ull;
+	auto mix = [&h]( const void *p, size_t n ) { const unsigned char *b = (const unsigned char *)p; for( size_t i = 0; i < n; i++ ) { h ^= b[i]; h *= 1099511628211ull; } };
+	mix( &D.sc, sizeof( D.sc ));
+	for( int j = 0; j < kn; j++ ) mix( &wss[j], sizeof( rc_work_t ));
+	const long long scal[] = { D.vw_grid, D.cache_aside, D.nbents, D.nbfaces, D.ntb, D.nitems, D.ntris, D.fast_tris, D.nfast_items, D.fast_maxcount, D.num_sms, kn };
+	mix( scal, sizeof( scal ));
+	return h ? h : 1;
+}
+
 /*
  * The device stages of the batch.  nslices == 1: one stream, stage boundaries optionally recorded in D.ev (the
  * per-kernel timings of the bench).  nslices > 1: the views are cut into slices, slice k on stream k % nstreams;
@@ -1071,7 +1142,7 @@ int run_batch( int nslices, int nstreams, bool timed, uint16_t *color_out, int16
 	rc_work_t &w = D.w;
 	cudaStream_t st = D.stream;
 	const size_t vpx = (size_t)w.width * w.height;
-	CK( cudaMemsetAsync( D.d_counters, 0, sizeof( unsigned long long ) * RC_CTR_COUNT, st ));
+	fill32( D.d_counters, 0u, 2 * RC_CTR_COUNT, st );
 	if( nslices > 1 && launch_studio_points( st ) != 0 ) return -1; /* ahead of the fork: every slice reads the result */
 	if( nslices <= 1 )
 	{
@@ -1079,30 +1150,76 @@ int run_batch( int nslices, int nstreams, bool timed, uint16_t *color_out, int16
 		if( launch_slice( ws, 0, st, timed ? D.ev : nullptr, true ) != 0 ) return -1;
 		if( color_out ) CK( cudaMemcpyAsync( color_out, w.color, (size_t)w.nviews * vpx * 2, cudaMemcpyDeviceToHost, st ));
 		if( z_out ) CK( cudaMemcpyAsync( z_out, w.zbuf, (size_t)w.nviews * vpx * 2, cudaMemcpyDeviceToHost, st ));
-		CK( cudaMemcpyAsync( D.h_counters, D.d_counters, sizeof( unsigned long long ) * RC_CTR_COUNT, cudaMemcpyDeviceToHost, st ));
+		k_counters_out<<<1, RC_CTR_COUNT, 0, st>>>( D.d_counters, D.h_counters_dev );
 		CK( cudaGetLastError());
 		return 0;
 	}
+	/*
+	 * The slices in pairs ("segments"): the two slices of a segment run side by side on the two slice streams, and the
+	 * frames of a finished segment leave on the copy stream while the next one is computed.  The ~30 launches of a segment
+	 * are replayed from a CUDA graph: while a copy engine is busy every single launch of the process takes longer (measured:
+	 * the stages of a batch 1.8x slower beside another stream's device->host copy; a 60-kernel graph 1.07x; a kernel that is
+	 * already running is not affected), and a batch with host outputs always has copies in flight.  A graph is keyed by a
+	 * hash of every launch argument (scene and slice records, the counts the grids are made from): any change re-captures it.
+	 */
 	if( timed ) CK( cudaEventRecord( D.ev[0], st ));
-	CK( cudaEventRecord( D.ev_fork, st ));
-	for( int p = 0; p < nstreams; p++ ) CK( cudaStreamWaitEvent( D.slice_stream[p], D.ev_fork, 0 ));
-	for( int k = 0; k < nslices; k++ )
+	const bool graphs = D.use_graphs && !timed && !D.sync_each && nstreams == 2 && !( nslices & 1 );
+	for( int k0 = 0; k0 < nslices; k0 += 2 )
 	{
-		const int v0 = (int)((long long)w.nviews * k / nslices ), v1 = (int)((long long)w.nviews * ( k + 1 ) / nslices );
-		cudaStream_t ss = D.slice_stream[k % nstreams];
-		const rc_work_t ws = make_slice( k, v0, v1 );
-		if( launch_slice( ws, k, ss, nullptr, true ) != 0 ) return -1;
-		CK( cudaEventRecord( D.ev_slice[k], ss ));
+		const int kn = k0 + 2 <= nslices ? 2 : 1;
+		int v0s[2], v1s[2];
+		rc_work_t wss[2];
+		for( int j = 0; j < kn; j++ )
+		{
+			v0s[j] = (int)((long long)w.nviews * ( k0 + j ) / nslices ); v1s[j] = (int)((long long)w.nviews * ( k0 + j + 1 ) / nslices );
+			wss[j] = make_slice( k0 + j, v0s[j], v1s[j] );
+		}
+		bool replayed = false;
+		if( graphs )
+		{
+			Dev::batch_graph_t &g = D.graphs[( k0 >> 1 ) & 3][D.use_alt ? 1 : 0];
+			const unsigned long long key = segment_key( wss, kn );
+			if( g.exec && g.key == key )
+				D.launches += g.launches;
+			else
+			{
+				if( g.exec ) { cudaGraphExecDestroy( g.exec ); g.exec = nullptr; }
+				const unsigned long long l0 = D.launches;
+				cudaGraph_t graph = nullptr;
+				bool ok = cudaStreamBeginCapture( st, cudaStreamCaptureModeThreadLocal ) == cudaSuccess;
+				if( ok )
+				{
+					ok = enqueue_segment( wss, k0, kn, st ) == 0;
+					ok = ( cudaStreamEndCapture( st, &graph ) == cudaSuccess ) && ok && graph;
+				}
+				if( ok ) ok = cudaGraphInstantiate( &g.exec, graph, 0 ) == cudaSuccess;
+				if( graph ) cudaGraphDestroy( graph );
+				if( !ok )
+				{
+					/* never seen; the plain path still works */
+					cudaGetLastError();
+					g.exec = nullptr; D.use_graphs = false; D.launches = l0;
+				}
+				else { g.key = key; g.launches = D.launches - l0; }
+			}
+			if( g.exec )
+			{
+				CK( cudaGraphLaunch( g.exec, st ));
+				replayed = true;
+			}
+		}
+		if( !replayed && enqueue_segment( wss, k0, kn, st ) != 0 ) return -1;
 		if( color_out || z_out )
 		{
-			CK( cudaStreamWaitEvent( D.copy, D.ev_slice[k], 0 ));
-			if( color_out ) CK( cudaMemcpyAsync( color_out + v0 * vpx, w.color + v0 * vpx, ( v1 - v0 ) * vpx * 2, cudaMemcpyDeviceToHost, D.copy ));
-			if( z_out ) CK( cudaMemcpyAsync( z_out + v0 * vpx, w.zbuf + v0 * vpx, ( v1 - v0 ) * vpx * 2, cudaMemcpyDeviceToHost, D.copy ));
+			CK( cudaEventRecord( D.ev_slice[k0], st ));
+			CK( cudaStreamWaitEvent( D.copy, D.ev_slice[k0], 0 ));
+			const size_t a0 = (size_t)v0s[0] * vpx, n = ( (size_t)v1s[kn - 1] - v0s[0] ) * vpx;
+			if( color_out ) CK( cudaMemcpyAsync( color_out + a0, w.color + a0, n * 2, cudaMemcpyDeviceToHost, D.copy ));
+			if( z_out ) CK( cudaMemcpyAsync( z_out + a0, w.zbuf + a0, n * 2, cudaMemcpyDeviceToHost, D.copy ));
 		}
-		CK( cudaStreamWaitEvent( st, D.ev_slice[k], 0 ));
 	}
 	if( timed ) CK( cudaEventRecord( D.ev[RC_BENCH_STAGES], st ));
-	CK( cudaMemcpyAsync( D.h_counters, D.d_counters, sizeof( unsigned long long ) * RC_CTR_COUNT, cudaMemcpyDeviceToHost, st ));
+	k_counters_out<<<1, RC_CTR_COUNT, 0, st>>>( D.d_counters, D.h_counters_dev );
 	CK( cudaGetLastError());
 	return 0;
 }
@@ -1113,6 +1230,11 @@ extern "C" {
 
 int rc_dev_init( int device )
 {
+	/* a batch with host outputs keeps 6 streams busy (stages of two slices, their surface-cache side streams, the copy stream,
+	 * the batch stream); the default of 8 hardware queues per device is shared with whatever else lives in the process, and
+	 * two streams on one queue serialise (measured: the second pair of slices ran 1.4x slower behind the first pair's
+	 * copies).  Only effective when the CUDA context does not exist yet; a host process that creates it first sets this itself */
+	setenv( "CUDA_DEVICE_MAX_CONNECTIONS", "32", 0 );
 	int n = 0;
 	if( !ck( cudaGetDeviceCount( &n ), "cudaGetDeviceCount" ) || n <= 0 )
 	{
@@ -1126,12 +1248,15 @@ int rc_dev_init( int device )
 	snprintf( D.name, sizeof( D.name ), "%s (sm_%d%d, %d SMs)", prop.name, prop.major, prop.minor, prop.multiProcessorCount );
 	D.device = device; D.num_sms = prop.multiProcessorCount;
 	D.sync_each = getenv( "RC_SYNC_EACH" ) != nullptr;
-	CK( cudaHostAlloc( (void **)&D.h_counters, sizeof( unsigned long long ) * RC_CTR_COUNT, cudaHostAllocDefault ));
+	CK( cudaHostAlloc( (void **)&D.h_counters, sizeof( unsigned long long ) * RC_CTR_COUNT, cudaHostAllocMapped ));
+	CK( cudaHostGetDevicePointer( (void **)&D.h_counters_dev, D.h_counters, 0 ));
 	memset( D.h_counters, 0, sizeof( unsigned long long ) * RC_CTR_COUNT );
 	CK( cudaStreamCreateWithFlags( &D.stream, cudaStreamNonBlocking ));
 	CK( cudaStreamCreateWithFlags( &D.copy, cudaStreamNonBlocking ));
 	for( auto &e : D.ev_slice ) CK( cudaEventCreateWithFlags( &e, cudaEventDisableTiming ));
 	CK( cudaEventCreateWithFlags( &D.ev_fork, cudaEventDisableTiming ));
+	for( auto &e : D.ev_join ) CK( cudaEventCreateWithFlags( &e, cudaEventDisableTiming ));
+	D.use_graphs = getenv( "RC_NO_GRAPHS" ) == nullptr;
 	for( auto &ss : D.slice_stream ) CK( cudaStreamCreateWithFlags( &ss, cudaStreamNonBlocking ));
 	for( auto &ss : D.aux_stream ) CK( cudaStreamCreateWithFlags( &ss, cudaStreamNonBlocking ));
 	for( auto &e : D.ev_cache ) { CK( cudaEventCreate( &e[0] )); CK( cudaEventCreate( &e[1] )); }
@@ -1161,6 +1286,8 @@ void rc_dev_shutdown( void )
 	for( void **p : ptrs ) { if( *p ) cudaFree( *p ); *p = nullptr; }
 	for( void *&p : D.d_scene ) { if( p ) cudaFree( p ); p = nullptr; }
 	if( D.h_counters ) { cudaFreeHost( D.h_counters ); D.h_counters = nullptr; }
+	for( auto &h : D.h_views ) { if( h ) cudaFreeHost( h ); h = nullptr; }
+	D.cap_hviews = 0;
 	D.cap_cands = D.cap_edges = D.cap_blk_events = 0; D.caps_dirty = false;
 	D.nitems = D.ncorners = D.nsortents = 0; D.h_items.clear(); D.ntris = 0; D.cap_item_order = D.cap_polys = 0;
 	D.nparts = D.totalverts = D.totalnorms = 0; D.cap_mvpos = D.cap_mlight = 0; D.studio_dirty = false;
@@ -1175,6 +1302,8 @@ void rc_dev_shutdown( void )
 	for( auto &e : D.ev ) { if( e ) cudaEventDestroy( e ); e = nullptr; }
 	for( auto &e : D.ev_cache ) for( auto &x : e ) { if( x ) cudaEventDestroy( x ); x = nullptr; }
 	if( D.ev_fork ) { cudaEventDestroy( D.ev_fork ); D.ev_fork = nullptr; }
+	for( auto &e : D.ev_join ) { if( e ) cudaEventDestroy( e ); e = nullptr; }
+	for( auto &row : D.graphs ) for( auto &g : row ) { if( g.exec ) cudaGraphExecDestroy( g.exec ); g.exec = nullptr; g.key = 0; }
 	D.launches = 0;
 	D.ready = false;
 }
@@ -1476,61 +1605,96 @@ int rc_dev_flush_cache( void )
 	return 0;
 }
 
+/* the per-batch buffers of the entity stages, sized for the batch capacity */
+static int ensure_entity_buffers( int width, int height )
+{
+	if( D.nbents )
+	{
+		const size_t need_l = (size_t)D.cap_views * D.sc.numleafs, need_b = (size_t)D.cap_views * ( D.w.nodewords + D.w.leafwords );
+		if( need_l > D.cap_leafbase ) { if( dalloc( &D.d_leafbase, need_l ) != 0 || dalloc( &D.d_leafkey, need_l ) != 0 ) return -1; D.cap_leafbase = need_l; }
+		const size_t need_t = (size_t)D.cap_views * D.ntb;
+		if( need_t > D.cap_tb )
+		{
+			if( dalloc( &D.d_tbsurfs, need_t * RC_TB_MAXSURFS ) != 0 || dalloc( &D.d_tbedges, need_t * RC_TB_MAXEDGES ) != 0 || dalloc( &D.d_tbcounts, need_t * 2 ) != 0 ) return -1;
+			D.cap_tb = need_t;
+		}
+		if( need_b > D.cap_bmvis ) { if( dalloc( &D.d_bmvis, need_b ) != 0 ) return -1; D.cap_bmvis = need_b; }
+		if( (size_t)D.cap_views > D.cap_viewbm ) { if( dalloc( &D.d_viewbm, (size_t)D.cap_views ) != 0 ) return -1; D.cap_viewbm = D.cap_views; }
+	}
+	if( D.nitems && ( D.ntris || D.ntb ))
+	{
+		const size_t need_v = (size_t)D.cap_views * D.nitems;
+		if( need_v > D.cap_itemvis ) { if( dalloc( &D.d_itemvis, need_v ) != 0 ) return -1; D.cap_itemvis = need_v; }
+		const size_t need_o = (size_t)D.cap_views * D.nitems, need_p = (size_t)D.cap_views * ( D.ntris - D.fast_tris ) + 1;
+		if( D.fast_tris )
+		{
+			const size_t need_k = (size_t)D.cap_views * width * height, need_b = (size_t)RC_MAX_SLICES * ( (size_t)D.cap_views * 4096 + 65536 );
+			if( need_k > D.cap_trikeys ) { if( dalloc( &D.d_trikeys, need_k ) != 0 ) return -1; D.cap_trikeys = need_k; }
+			if( need_b > D.cap_big ) { if( dalloc( &D.d_biglist, 2 * need_b ) != 0 ) return -1; D.cap_big = need_b; }
+			const size_t need_pr = (size_t)D.cap_views * D.nfast_items;
+			if( need_pr > D.cap_pairs ) { if( dalloc( &D.d_pairs, need_pr ) != 0 ) return -1; D.cap_pairs = need_pr; }
+		}
+		if( need_o > D.cap_item_order ) { if( dalloc( &D.d_item_order, need_o ) != 0 ) return -1; D.cap_item_order = need_o; }
+		if( need_p > D.cap_polys ) { if( dalloc( &D.d_polys, need_p ) != 0 ) return -1; D.cap_polys = need_p; }
+	}
+	return 0;
+}
+
+/* the batch's per-view constants to the device; buffers zeroed where the views leave a border */
+static int begin_batch( const rc_view_t *views, int nviews, int width, int height, int clear )
+{
+	rc_work_t &w = D.w;
+	w.nviews = nviews; w.clear = clear;
+	cudaStream_t st = D.stream;
+	if( (size_t)nviews > D.cap_hviews )
+	{
+		CK( cudaStreamSynchronize( st ));
+		for( auto &h : D.h_views ) { if( h ) cudaFreeHost( h ); h = nullptr; }
+		const size_t cap = (size_t)nviews > (size_t)D.cap_views ? (size_t)nviews : (size_t)D.cap_views;
+		for( auto &h : D.h_views ) CK( cudaHostAlloc( (void **)&h, sizeof( rc_view_t ) * cap, cudaHostAllocMapped ));
+		D.cap_hviews = cap;
+	}
+	{
+		static_assert( sizeof( rc_view_t ) % 4 == 0, "rc_view_t is copied in 32-bit words" );
+		rc_view_t *stage = D.h_views[D.hviews_turn ^= 1];
+		memcpy( stage, views, sizeof( rc_view_t ) * nviews );
+		uint32_t *stage_dev = nullptr;
+		CK( cudaHostGetDevicePointer( (void **)&stage_dev, stage, 0 ));
+		const size_t nwords = sizeof( rc_view_t ) / 4 * (size_t)nviews;
+		k_copy32<<<(unsigned)(( nwords + 255 ) / 256 < 592 ? ( nwords + 255 ) / 256 : 592 ), 256, 0, st>>>( (uint32_t *)D.d_views, stage_dev, nwords );
+	}
+	D.h2d_bytes += sizeof( rc_view_t ) * (size_t)nviews;
+	size_t px = (size_t)nviews * width * height;
+	if( clear )
+	{
+		/* views that do not cover the whole buffer leave a border the span pass never touches */
+		bool full = true;
+		for( int i = 0; i < nviews && full; i++ )
+			full = views[i].vrect[0] == 0 && views[i].vrect[1] == 0 && views[i].vrect[2] == width && views[i].vrect[3] == height;
+		if( !full )
+		{
+			fill32( w.color, 0u, ( px + 1 ) / 2, st ); /* the buffers hold cap_views frames of an even pixel count or end on allocation slack */
+			fill32( w.zbuf, 0u, ( px + 1 ) / 2, st );
+		}
+	}
+	return 0;
+}
+
+int rc_dev_wait( void );
+
 int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, int clear, uint16_t *color_out, int16_t *z_out )
 {
 	if( !D.ready ) { snprintf( D.err, sizeof( D.err ), "device not initialised" ); return -1; }
 	if( !D.sc.numsurfaces || !D.sc.surfaces ) { snprintf( D.err, sizeof( D.err ), "no world uploaded" ); return -1; }
 	if( nviews <= 0 || width <= 0 || height <= 0 || height > 1200 ) { snprintf( D.err, sizeof( D.err ), "bad batch geometry" ); return -1; }
+	if( rc_dev_wait() != 0 ) return -1; /* an asynchronous batch still in flight finishes first */
 	for( int attempt = 0; ; attempt++ )
 	{
 		if( ensure_batch( nviews, width, height ) != 0 ) return -1;
-		if( D.nbents )
-		{
-			const size_t need_l = (size_t)D.cap_views * D.sc.numleafs, need_b = (size_t)D.cap_views * ( D.w.nodewords + D.w.leafwords );
-			if( need_l > D.cap_leafbase ) { if( dalloc( &D.d_leafbase, need_l ) != 0 || dalloc( &D.d_leafkey, need_l ) != 0 ) return -1; D.cap_leafbase = need_l; }
-			const size_t need_t = (size_t)D.cap_views * D.ntb;
-			if( need_t > D.cap_tb )
-			{
-				if( dalloc( &D.d_tbsurfs, need_t * RC_TB_MAXSURFS ) != 0 || dalloc( &D.d_tbedges, need_t * RC_TB_MAXEDGES ) != 0 || dalloc( &D.d_tbcounts, need_t * 2 ) != 0 ) return -1;
-				D.cap_tb = need_t;
-			}
-			if( need_b > D.cap_bmvis ) { if( dalloc( &D.d_bmvis, need_b ) != 0 ) return -1; D.cap_bmvis = need_b; }
-			if( (size_t)D.cap_views > D.cap_viewbm ) { if( dalloc( &D.d_viewbm, (size_t)D.cap_views ) != 0 ) return -1; D.cap_viewbm = D.cap_views; }
-		}
-		if( D.nitems && ( D.ntris || D.ntb ))
-		{
-			const size_t need_v = (size_t)D.cap_views * D.nitems;
-			if( need_v > D.cap_itemvis ) { if( dalloc( &D.d_itemvis, need_v ) != 0 ) return -1; D.cap_itemvis = need_v; }
-			const size_t need_o = (size_t)D.cap_views * D.nitems, need_p = (size_t)D.cap_views * ( D.ntris - D.fast_tris ) + 1;
-			if( D.fast_tris )
-			{
-				const size_t need_k = (size_t)D.cap_views * width * height, need_b = (size_t)RC_MAX_SLICES * ( (size_t)D.cap_views * 4096 + 65536 );
-				if( need_k > D.cap_trikeys ) { if( dalloc( &D.d_trikeys, need_k ) != 0 ) return -1; D.cap_trikeys = need_k; }
-				if( need_b > D.cap_big ) { if( dalloc( &D.d_biglist, 2 * need_b ) != 0 ) return -1; D.cap_big = need_b; }
-				const size_t need_pr = (size_t)D.cap_views * D.nfast_items;
-				if( need_pr > D.cap_pairs ) { if( dalloc( &D.d_pairs, need_pr ) != 0 ) return -1; D.cap_pairs = need_pr; }
-			}
-			if( need_o > D.cap_item_order ) { if( dalloc( &D.d_item_order, need_o ) != 0 ) return -1; D.cap_item_order = need_o; }
-			if( need_p > D.cap_polys ) { if( dalloc( &D.d_polys, need_p ) != 0 ) return -1; D.cap_polys = need_p; }
-		}
-		rc_work_t &w = D.w;
-		w.nviews = nviews; w.clear = clear;
+		D.w.color = D.main_color; D.w.zbuf = D.main_zbuf; D.use_alt = false;
+		if( ensure_entity_buffers( width, height ) != 0 ) return -1;
+		if( begin_batch( views, nviews, width, height, clear ) != 0 ) return -1;
 		cudaStream_t st = D.stream;
-		CK( cudaMemcpyAsync( D.d_views, views, sizeof( rc_view_t ) * nviews, cudaMemcpyHostToDevice, st ));
-		D.h2d_bytes += sizeof( rc_view_t ) * (size_t)nviews;
-		size_t px = (size_t)nviews * width * height;
-		if( clear )
-		{
-			/* views that do not cover the whole buffer leave a border the span pass never touches */
-			bool full = true;
-			for( int i = 0; i < nviews && full; i++ )
-				full = views[i].vrect[0] == 0 && views[i].vrect[1] == 0 && views[i].vrect[2] == width && views[i].vrect[3] == height;
-			if( !full )
-			{
-				CK( cudaMemsetAsync( w.color, 0, px * 2, st ));
-				CK( cudaMemsetAsync( w.zbuf, 0, px * 2, st ));
-			}
-		}
 		{
 			/* frames that go back to the host: 4 slices of views on two streams, so that the copies of the first pair
 			 * overlap the stages of the second (the copies are the long pole: PCIe).  Frames that stay in HBM: one
@@ -1551,8 +1715,75 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 	}
 }
 
+
+/*
+ * Asynchronous batches.  rc_dev_render_async enqueues everything rc_dev_render does - stages per view slice, the frames of
+ * every slice copied to the host on the copy stream - and returns; the frames are in color_out / z_out after rc_dev_wait.
+ * Successive asynchronous batches draw into alternating sets of frame buffers, so the copies of batch k (PCIe, the long
+ * pole) run under the stages of batch k + 1.  Before a new batch is enqueued the kernels (not the copies) of the previous
+ * one are waited for and its overflow counters checked; a batch that overflowed a capacity is rendered again, synchronously.
+ */
+static int settle_pending()
+{
+	if( !D.pending )
+		return 0;
+	CK( cudaEventSynchronize( D.ev_kdone ));
+	D.pending = false;
+	const int again = check_capacities();
+	if( again < 0 ) return -1;
+	if( !again ) return 0;
+	CK( cudaStreamSynchronize( D.copy ));
+	std::vector<rc_view_t> v;
+	v.swap( D.pend_views );
+	return rc_dev_render( v.data(), (int)v.size(), D.pend_w, D.pend_h, D.pend_clear, D.pend_color, D.pend_z );
+}
+
+int rc_dev_wait( void )
+{
+	if( !D.ready ) return 0;
+	if( settle_pending() != 0 ) return -1;
+	CK( cudaStreamSynchronize( D.copy ));
+	CK( cudaStreamSynchronize( D.stream ));
+	return 0;
+}
+
+int rc_dev_render_async( const rc_view_t *views, int nviews, int width, int height, int clear, uint16_t *color_out, int16_t *z_out )
+{
+	if( !D.ready ) { snprintf( D.err, sizeof( D.err ), "device not initialised" ); return -1; }
+	/* nothing to overlap (frames stay in HBM, or depend on the previous batch's pixels, or too few views to slice) */
+	if( !clear || ( !color_out && !z_out ) || nviews < 16 * RC_MAX_SLICES || width <= 0 || height <= 0 || height > 1200 || !D.sc.numsurfaces )
+		return rc_dev_render( views, nviews, width, height, clear, color_out, z_out );
+	if( settle_pending() != 0 ) return -1;
+	if( nviews > D.cap_views || width != D.cap_w || height != D.cap_h || D.caps_dirty )
+	{
+		if( rc_dev_wait() != 0 ) return -1; /* buffers are about to be replaced: nothing may be in flight */
+		if( ensure_batch( nviews, width, height ) != 0 ) return -1;
+	}
+	if( ensure_entity_buffers( width, height ) != 0 ) return -1;
+	const size_t px = (size_t)D.cap_views * width * height;
+	if( D.alt_px < px )
+	{
+		if( rc_dev_wait() != 0 ) return -1;
+		if( dalloc( &D.alt_color, px ) != 0 || dalloc( &D.alt_zbuf, px ) != 0 ) return -1;
+		D.alt_px = px;
+	}
+	D.use_alt = !D.use_alt;
+	D.w.color = D.use_alt ? D.alt_color : D.main_color;
+	D.w.zbuf = D.use_alt ? D.alt_zbuf : D.main_zbuf;
+	if( begin_batch( views, nviews, width, height, clear ) != 0 ) return -1;
+	if( run_batch( RC_MAX_SLICES, 2, false, color_out, z_out ) != 0 ) return -1;
+	if( !D.ev_kdone ) CK( cudaEventCreateWithFlags( &D.ev_kdone, cudaEventDisableTiming ));
+	CK( cudaEventRecord( D.ev_kdone, D.stream ));
+	D.pend_views.assign( views, views + nviews );
+	D.pend_w = width; D.pend_h = height; D.pend_clear = clear; D.pend_color = color_out; D.pend_z = z_out;
+	D.pending = true;
+	D.have_batch = true;
+	return 0;
+}
+
 int rc_dev_bench_resident( int iters, int flags, float *ms_total, float *ms_stage )
 {
+	if( rc_dev_wait() != 0 ) return -1;
 	if( !D.have_batch ) { snprintf( D.err, sizeof( D.err ), "no batch rendered yet" ); return -1; }
 	float tot = 0, stage[RC_BENCH_STAGES] = { 0 };
 	bool overlapped = false;

@@ -2079,7 +2079,7 @@ static void R_EndFrame( void )
 
 /* ---- batch extension (include/ref_cuda.h) ---- */
 
-int RefCuda_RenderViews( const ref_viewpass_t *views, int nviews, unsigned short *color_out, short *z_out, int clear )
+static int rc_render_views( const ref_viewpass_t *views, int nviews, unsigned short *color_out, short *z_out, int clear, qboolean async )
 {
 	if( !rc.initialized || nviews <= 0 )
 		return -1;
@@ -2088,12 +2088,31 @@ int RefCuda_RenderViews( const ref_viewpass_t *views, int nviews, unsigned short
 	rc.nviews = 0;
 	for( int i = 0; i < nviews; i++ )
 		rc_queue_view( &views[i] );
-	int r = rc_dev_render( rc.views, rc.nviews, gpGlobals->width, gpGlobals->height, clear, color_out, z_out );
+	int r = ( async ? rc_dev_render_async : rc_dev_render )( rc.views, rc.nviews, gpGlobals->width, gpGlobals->height, clear, color_out, z_out );
 	rc.nviews = 0;
 	rc.last_h2d = rc_dev_h2d_bytes( 0 );
 	if( r != 0 )
 		gEngfuncs.Host_Error( "ref_cuda: rc_dev_render failed: %s\n", rc_dev_last_error());
 	return r;
+}
+
+int RefCuda_RenderViews( const ref_viewpass_t *views, int nviews, unsigned short *color_out, short *z_out, int clear )
+{
+	return rc_render_views( views, nviews, color_out, z_out, clear, false );
+}
+
+int RefCuda_RenderViewsAsync( const ref_viewpass_t *views, int nviews, unsigned short *color_out, short *z_out, int clear )
+{
+	return rc_render_views( views, nviews, color_out, z_out, clear, true );
+}
+
+int RefCuda_Wait( void )
+{
+	if( !rc.initialized )
+		return -1;
+	if( rc_dev_wait() != 0 )
+		gEngfuncs.Host_Error( "ref_cuda: rc_dev_wait failed: %s\n", rc_dev_last_error());
+	return 0;
 }
 
 int RefCuda_BenchResident( int iters, int flags, float *ms_total, float *ms_stage )

@@ -60,6 +60,8 @@ class Renderer:
         if self.is_cuda:
             sym = self.host.symbol
             self._render = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int)(sym("RefCuda_RenderViews"))
+            self._render_async = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int)(sym("RefCuda_RenderViewsAsync"))
+            self._wait = C.CFUNCTYPE(C.c_int)(sym("RefCuda_Wait"))
             self._bench = C.CFUNCTYPE(C.c_int, C.c_int, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_float))(sym("RefCuda_BenchResident"))
             self._readcache = C.CFUNCTYPE(C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int))(sym("RefCuda_ReadSurfaceCache"))
             self._counters = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int)(sym("RefCuda_GetCounters"))
@@ -261,6 +263,15 @@ class Renderer:
         """RefCuda_RenderViews on a prebuilt ref_viewpass_t array and raw host pointers (bench e2e leg)."""
         if self._render(C.addressof(vp), len(vp), color_ptr, z_ptr, 1 if clear else 0) != 0:
             raise RuntimeError("RefCuda_RenderViews failed")
+
+    def render_prepared_async(self, vp, color_ptr, z_ptr, clear=True):
+        """RefCuda_RenderViewsAsync: enqueued only; the host buffers are complete after wait()"""
+        if self._render_async(C.addressof(vp), len(vp), color_ptr, z_ptr, 1 if clear else 0) != 0:
+            raise RuntimeError("RefCuda_RenderViewsAsync failed")
+
+    def wait(self):
+        if self._wait() != 0:
+            raise RuntimeError("RefCuda_Wait failed")
 
     def bench_resident(self, iters, rebuild_cache=False, flush_l2=False, overlap=False, serial_cache=False):
         """CUDA-event ms per iteration of the last batch re-run with inputs resident in HBM: (total, [6 stages: vis_walk,
