@@ -23,6 +23,7 @@
 #include <string.h>
 #include <time.h>
 
+#include <map>
 #include <vector>
 
 #include "rc_dev.h"
@@ -781,6 +782,24 @@ template <typename T> int upload( T **dst, const T *src, size_t n )
 	return 0;
 }
 
+/* per-batch state (entity lists, bones): the buffer is kept and only grows - cudaFree / cudaMalloc synchronise the whole
+ * device, which would wait for the frames an earlier asynchronous batch is still copying to the host */
+template <typename T> int upload_keep( T **dst, const T *src, size_t n )
+{
+	static std::map<void **, size_t> caps; /* capacity (elements) of the buffer behind every pointer slot */
+	size_t &cap = caps[(void **)dst];
+	if( !*dst ) cap = 0;
+	if( n > cap || !*dst )
+	{
+		const size_t want = n + n / 2 + 16;
+		if( *dst ) { cudaFree( *dst ); *dst = nullptr; }
+		CK( cudaMalloc( (void **)dst, sizeof( T ) * want ));
+		cap = want;
+	}
+	if( n && src ) CK( cudaMemcpy( *dst, src, sizeof( T ) * n, cudaMemcpyHostToDevice ));
+	return 0;
+}
+
 template <typename T> int dalloc( T **dst, size_t n )
 {
 	if( *dst ) { cudaFree( *dst ); *dst = nullptr; }
@@ -1475,9 +1494,9 @@ int rc_dev_set_items( const rc_item_t *items, int nitems, const rc_corner_t *cor
 	CK( cudaStreamSynchronize( D.stream ));
 	D.nitems = nitems; D.nsortents = nsortents; D.ncorners = ncorners;
 	if( !nitems ) { D.ntris = 0; return 0; }
-	if( upload( &D.d_items, items, (size_t)nitems ) != 0 ) return -1;
-	if( upload( &D.d_corners, corners, (size_t)ncorners ) != 0 ) return -1;
-	if( upload( &D.d_sortents, sortents, (size_t)nsortents ) != 0 ) return -1;
+	if( upload_keep( &D.d_items, items, (size_t)nitems ) != 0 ) return -1;
+	if( upload_keep( &D.d_corners, corners, (size_t)ncorners ) != 0 ) return -1;
+	if( upload_keep( &D.d_sortents, sortents, (size_t)nsortents ) != 0 ) return -1;
 	D.h_items.assign( items, items + nitems );
 	D.ntris = 0;
 	for( int i = 0; i < nitems; i++ ) D.ntris += items[i].count;
@@ -1499,13 +1518,13 @@ int rc_dev_set_bents( const rc_bent_t *bents, int n )
 	std::vector<int32_t> bf;
 	for( int e = 0; e < n; e++ )
 		for( int f = 0; !bents[e].trans && f < bents[e].numfaces && f < 65536; f++ ) bf.push_back(( e << 16 ) | f );
-	if( upload( &D.d_bents, bents, (size_t)n ) != 0 ) return -1;
-	if( upload( &D.d_bfaces, bf.data(), bf.size()) != 0 ) return -1;
+	if( upload_keep( &D.d_bents, bents, (size_t)n ) != 0 ) return -1;
+	if( upload_keep( &D.d_bfaces, bf.data(), bf.size()) != 0 ) return -1;
 	D.h2d_bytes += sizeof( rc_bent_t ) * (size_t)n + 4 * bf.size();
 	std::vector<int32_t> ord( n );
 	int ntb = 0;
 	for( int e = 0; e < n; e++ ) ord[e] = bents[e].trans ? ntb++ : -1;
-	if( upload( &D.d_tbord, ord.data(), ord.size()) != 0 ) return -1;
+	if( upload_keep( &D.d_tbord, ord.data(), ord.size()) != 0 ) return -1;
 	D.ntb = ntb;
 	D.nbents = n; D.nbfaces = (int)bf.size();
 	return 0;
@@ -1544,9 +1563,9 @@ int rc_dev_set_studio( const rc_spart_t *parts, int nparts, const float *bones, 
 	CK( cudaStreamSynchronize( D.stream ));
 	D.nparts = nparts; D.totalverts = totalverts; D.totalnorms = totalnorms;
 	if( !nparts ) return 0;
-	if( upload( &D.d_parts, parts, (size_t)nparts ) != 0 ) return -1;
-	if( upload( &D.d_bones, bones, (size_t)nbones * 12 ) != 0 ) return -1;
-	if( upload( &D.d_blight, blightvecs, (size_t)nbones * 3 ) != 0 ) return -1;
+	if( upload_keep( &D.d_parts, parts, (size_t)nparts ) != 0 ) return -1;
+	if( upload_keep( &D.d_bones, bones, (size_t)nbones * 12 ) != 0 ) return -1;
+	if( upload_keep( &D.d_blight, blightvecs, (size_t)nbones * 3 ) != 0 ) return -1;
 	if( (size_t)totalverts * 3 > D.cap_mvpos ) { if( dalloc( &D.d_mvpos, (size_t)totalverts * 3 ) != 0 ) return -1; D.cap_mvpos = (size_t)totalverts * 3; }
 	if( (size_t)totalnorms > D.cap_mlight ) { if( dalloc( &D.d_mlight, (size_t)totalnorms ) != 0 ) return -1; D.cap_mlight = (size_t)totalnorms; }
 	D.h2d_bytes += sizeof( rc_spart_t ) * (size_t)nparts + sizeof( float ) * 15 * (size_t)nbones;
