@@ -6,7 +6,9 @@
  *   S0 k_viswalk      Mod_PointInLeaf/Mod_FatPVS/R_MarkLeaves + R_RecursiveWorldNode   one block per view (rc_k_vis.cuh)
  *   S1 k_faces        R_RenderFace/R_ClipEdge/R_EmitEdge + D_CalcGradients             one thread per (view, face)
  *   S2 k_cache_list   D_CacheSurface staleness test -> work list                        one thread per (face, mip)
- *      k_cache_build  R_BuildLightMap (+ R_AddDynamicLights) + R_DrawSurface            persistent CTAs, one block per (face, mip)
+ *      k_cache_light  R_BuildLightMap (+ R_AddDynamicLights), light-block source offsets   warp per listed (face, mip)
+ *      k_cache_texels R_DrawSurface / R_DrawSurfaceBlock8_mipN                            CTA per 256 runs of 8 / 4 / 2 texels, flat over all items
+ *      k_cache_build  the same for blocks that are not made of whole light blocks          persistent CTAs, one block per (face, mip)
  *      k_dlight_mark  R_PushDlights/R_MarkLights                                        one thread per face, once per light set
  *   S3 k_events/k_lines R_ScanEdges/R_GenerateSpans (rc_k_spans.cuh)                    lane per scanline / warp per scanline
  *      k_draw         D_DrawSpans16/D_DrawZSpans/Turbulent8/D_BackgroundSurf (rc_k_draw.cuh) one warp per group of scanlines
@@ -64,6 +66,12 @@ struct rc_work_t
 	uint32_t  *cache_need;/* [numsurfaces * 4 bits] */
 	rc_cachekey_t *cache_keys; /* [numsurfaces * 4] */
 	int32_t   *cache_list;/* [numsurfaces * 4] work list of surf * 4 + mip */
+	/* the flat path of the surface cache (k_cache_light / k_cache_texels): (face, mip) blocks made of whole light blocks */
+	int32_t   *cache_flist;   /* [numsurfaces * 4] their slots */
+	uint32_t  *cache_units;   /* [numsurfaces * 4 * 32] pieces of 256 runs: position in cache_flist << 6 | piece */
+	uint32_t  *cache_lux;     /* [numsurfaces * 4][CACHE_FLUX] blocklights of the item (rc_blocklight) */
+	int32_t   *cache_src;     /* [numsurfaces * 4][CACHE_FLUX] source offset of every light block (the reference's wrap rules) */
+	int32_t   *cache_fn;      /* [0] items in cache_flist, [1] pieces in cache_units */
 	int32_t   *cache_nlist, *cache_cursor;
 	int32_t   *line_cursor; /* k_lines work cursors: heavy list, all lines */
 	int32_t   *heavy_list, *heavy_count; /* [nviews * height] lines with more than LN_HEAVY events (k_events), their number */
@@ -364,6 +372,25 @@ __device__ __forceinline__ bool rc_key_stale( const rc_cachekey_t *k, const rc_s
 	return false;
 }
 
+#define CACHE_FLUX 256 /* luxels / light blocks of an item the flat path takes (a 16 x 16 lightmap: faces up to 240 texels) */
+
+/* geometry of a (face, mip) block; fast = made of whole light blocks (every face whose extents are multiples of 16) */
+struct rc_cacheitem_t { int32_t smax, tmax, size, bw, bh, nbu, nbv, rl, nruns; bool fast; };
+__device__ __forceinline__ rc_cacheitem_t rc_cache_item( const rc_surface_t *sf, int32_t mip )
+{
+	rc_cacheitem_t c;
+	c.smax = sf->lightextents[0] / sf->sample_size + 1; c.tmax = sf->lightextents[1] / sf->sample_size + 1;
+	c.size = c.smax * c.tmax;
+	c.bw = sf->lightextents[0] >> mip; c.bh = sf->lightextents[1] >> mip;
+	const int32_t k = 4 - mip, bs = 16 >> mip;
+	c.nbu = c.bw >> k; c.nbv = c.bh >> k;
+	c.rl = mip <= 1 ? 8 : ( mip == 2 ? 4 : 2 );
+	c.nruns = ( c.bw / c.rl ) * c.bh;
+	c.fast = c.nbu * bs == c.bw && c.nbv * bs == c.bh && c.nbu < c.smax && c.nbv < c.tmax && c.size <= CACHE_FLUX && c.nbu * c.nbv <= CACHE_FLUX
+		&& c.nruns > 0 && c.nruns <= 32 * 256;
+	return c;
+}
+
 __global__ void __launch_bounds__( 256 ) k_cache_list( rc_scene_t sc, rc_work_t w )
 {
 	const int slot = blockIdx.x * blockDim.x + threadIdx.x;
@@ -375,8 +402,69 @@ __global__ void __launch_bounds__( 256 ) k_cache_list( rc_scene_t sc, rc_work_t 
 	if( sf->cache_ofs[slot & 3] < 0 )
 		return;
 	/* a face lit by a dynamic light is rebuilt every frame, and so is a block that was built with one */
-	if( rc_key_stale( &w.cache_keys[slot], sf, w.styles ) || w.cache_keys[slot].dlight || ( w.ndlights && w.dlightbits[slot >> 2] ))
-		w.cache_list[atomicAdd( w.cache_nlist, 1 )] = slot;
+	if( !( rc_key_stale( &w.cache_keys[slot], sf, w.styles ) || w.cache_keys[slot].dlight || ( w.ndlights && w.dlightbits[slot >> 2] )))
+		return;
+	const rc_cacheitem_t c = rc_cache_item( sf, slot & 3 );
+	if( !c.fast )
+	{
+		w.cache_list[atomicAdd( w.cache_nlist, 1 )] = slot; /* ragged blocks: k_cache_build, a CTA per item */
+		return;
+	}
+	const int32_t pos = atomicAdd( &w.cache_fn[0], 1 );
+	w.cache_flist[pos] = slot;
+	const int32_t npieces = ( c.nruns + 255 ) >> 8;
+	const int32_t u0 = atomicAdd( &w.cache_fn[1], npieces );
+	for( int32_t u = 0; u < npieces; u++ ) w.cache_units[u0 + u] = ((uint32_t)pos << 6 ) | (uint32_t)u;
+}
+
+/* blocklights and light-block source offsets of every listed item: a warp per item, lanes over the luxels / blocks */
+__global__ void __launch_bounds__( 256 ) k_cache_light( rc_scene_t sc, rc_work_t w )
+{
+	const int lane = threadIdx.x & 31;
+	const int32_t n = w.cache_fn[0], nwarps = gridDim.x * ( blockDim.x >> 5 );
+	for( int32_t it = blockIdx.x * ( blockDim.x >> 5 ) + ( threadIdx.x >> 5 ); it < n; it += nwarps )
+	{
+		const int32_t slot = w.cache_flist[it], mip = slot & 3;
+		const rc_surface_t *sf = &sc.surfaces[slot >> 2];
+		const rc_texture_t *tex = &sc.textures[sf->texnum];
+		const rc_cacheitem_t c = rc_cache_item( sf, mip );
+		const uint32_t dbits = w.ndlights ? w.dlightbits[slot >> 2] : 0u;
+		uint32_t *lux = w.cache_lux + (size_t)slot * CACHE_FLUX;
+		for( int32_t i = lane; i < c.size; i += 32 )
+		{
+			uint32_t extra = 0;
+			if( dbits )
+			{
+				const int32_t lt = i / c.smax;
+				extra = rc_dlight_luxel( &sc, sf, w.dlights, w.ndlights, dbits, i - lt * c.smax, lt );
+			}
+			lux[i] = rc_blocklight( &sc, sf, w.styles, c.size, i, extra );
+		}
+		/* source offset of every light block: the column offset advances per block column and snaps to 0 past the texture
+		 * width, the row offset advances per block row and steps back by the texture size (r_surf.c:411-426,586-600) */
+		const int32_t bs = 16 >> mip;
+		int32_t smaxt = tex->width >> mip, tmaxt = tex->height >> mip;
+		if( smaxt < 1 ) smaxt = 1;
+		if( tmaxt < 1 ) tmaxt = 1;
+		const int32_t total = tmaxt * smaxt;
+		int32_t *srcofs = w.cache_src + (size_t)slot * CACHE_FLUX;
+		for( int32_t bu = lane; bu < c.nbu; bu += 32 )
+		{
+			int32_t soffset = ((( (int32_t)sf->lightmapmins[0] ) >> mip ) + ( smaxt << 16 )) % smaxt;
+			for( int32_t q = 0; q < bu; q++ )
+			{
+				soffset += bs;
+				if( soffset >= smaxt ) soffset = 0;
+			}
+			int32_t rowofs = (((( (int32_t)sf->lightmapmins[1] ) >> mip ) + ( tmaxt << 16 )) % tmaxt ) * smaxt;
+			for( int32_t bv = 0; bv < c.nbv; bv++ )
+			{
+				srcofs[bv * c.nbu + bu] = rowofs + soffset;
+				rowofs += bs * smaxt;
+				if( rowofs + soffset >= total ) rowofs -= total;
+			}
+		}
+	}
 }
 
 /*
@@ -386,46 +474,104 @@ __global__ void __launch_bounds__( 256 ) k_cache_list( rc_scene_t sc, rc_work_t 
  * reference's psource after its column / row wrap rules, rc_cache_texel).
  */
 template <int RL>
+__device__ __forceinline__ void rc_cache_run( const uint16_t *__restrict__ src, const uint16_t *__restrict__ cmap, int32_t lim, int32_t smaxt, int32_t mip,
+	const uint32_t *bl, int32_t lightwidth, const int32_t *rc, int32_t nbu, uint16_t *dst, int32_t bw, int32_t rpr, int32_t r )
+{
+	const int32_t k = 4 - mip, bs = 16 >> mip;
+	const int32_t y = r / rpr, x = ( r - y * rpr ) * RL;
+	const int32_t bu = x >> k, b0 = x & ( bs - 1 ), bv = y >> k, i = y & ( bs - 1 );
+	const uint32_t *lp = bl + bv * lightwidth + bu;
+	uint32_t ll = lp[0], lr = lp[1];
+	const uint32_t lls = ( lp[lightwidth] - ll ) >> k, lrs = ( lp[lightwidth + 1] - lr ) >> k;
+	ll += (uint32_t)i * lls; lr += (uint32_t)i * lrs;
+	const uint32_t step = ( ll - lr ) >> k;
+	uint32_t light = lr + (uint32_t)( bs - 1 - b0 ) * step;
+	const int32_t idx0 = rc[bv * nbu + bu] + i * smaxt + b0;
+	uint32_t packed[RL / 2];
+#pragma unroll
+	for( int j = 0; j < RL; j++ )
+	{
+		/* the reference reads past the mip when a texture is not a multiple of the block size; stay inside the arena */
+		int32_t idx = idx0 + j;
+		idx = idx < 0 ? 0 : ( idx >= lim ? lim - 1 : idx );
+		const uint32_t pix = __ldg( src + idx );
+		uint32_t o = (uint32_t)__ldg( cmap + (( pix >> 3 ) | (( light & 0x1f00u ) << 5 ))) | ( pix & 7u );
+		if( mip == 0 && pix == RC_TRANSPARENT_COLOR )
+			o = RC_TRANSPARENT_COLOR;
+		if( j & 1 ) packed[j >> 1] |= o << 16; else packed[j >> 1] = o;
+		light -= step;
+	}
+	uint16_t *out = dst + (size_t)y * bw + x;
+	if( RL == 8 ) *reinterpret_cast<uint4 *>( out ) = make_uint4( packed[0], packed[1], packed[2 % ( RL / 2 )], packed[3 % ( RL / 2 )] );
+	else if( RL == 4 ) *reinterpret_cast<uint2 *>( out ) = make_uint2( packed[0], packed[1 % ( RL / 2 )] );
+	else *reinterpret_cast<uint32_t *>( out ) = packed[0];
+}
+
+template <int RL>
 __device__ __forceinline__ void rc_cache_runs( const rc_scene_t &sc, const rc_texture_t *tex, int32_t mip, const uint32_t *s_bl, int32_t lightwidth,
 	const int32_t *s_rc, int32_t nbu, uint16_t *dst, int32_t bw, int32_t bh, int tid )
 {
-	const int32_t k = 4 - mip, bs = 16 >> mip;
 	int32_t smaxt = tex->width >> mip;
 	if( smaxt < 1 ) smaxt = 1;
 	const int32_t lim = tex->width * tex->height * 2;
 	const uint16_t *__restrict__ src = sc.texels + tex->ofs[mip];
-	const uint16_t *__restrict__ cmap = sc.colormap;
 	const int32_t rpr = bw / RL, total = rpr * bh;
-
 	for( int32_t r = tid; r < total; r += CACHE_THREADS )
+		rc_cache_run<RL>( src, sc.colormap, lim, smaxt, mip, s_bl, lightwidth, s_rc, nbu, dst, bw, rpr, r );
+}
+
+/* the texels of the listed items, flat: a CTA per piece of 256 runs, a thread per run of 8 / 4 / 2 texels of one row of one
+ * light block (one 16 / 8 / 4-byte store); blocklights and source offsets come from k_cache_light's tables (L1 / L2) */
+__global__ void __launch_bounds__( 256 ) k_cache_texels( rc_scene_t sc, rc_work_t w )
+{
+	const int32_t npieces = w.cache_fn[1];
+	for( int32_t u = blockIdx.x; u < npieces; u += gridDim.x )
 	{
-		const int32_t y = r / rpr, x = ( r - y * rpr ) * RL;
-		const int32_t bu = x >> k, b0 = x & ( bs - 1 ), bv = y >> k, i = y & ( bs - 1 );
-		const uint32_t *lp = s_bl + bv * lightwidth + bu;
-		uint32_t ll = lp[0], lr = lp[1];
-		const uint32_t lls = ( lp[lightwidth] - ll ) >> k, lrs = ( lp[lightwidth + 1] - lr ) >> k;
-		ll += (uint32_t)i * lls; lr += (uint32_t)i * lrs;
-		const uint32_t step = ( ll - lr ) >> k;
-		uint32_t light = lr + (uint32_t)( bs - 1 - b0 ) * step;
-		const int32_t idx0 = s_rc[bv * nbu + bu] + i * smaxt + b0;
-		uint32_t packed[RL / 2];
-#pragma unroll
-		for( int j = 0; j < RL; j++ )
-		{
-			/* the reference reads past the mip when a texture is not a multiple of the block size; stay inside the arena */
-			int32_t idx = idx0 + j;
-			idx = idx < 0 ? 0 : ( idx >= lim ? lim - 1 : idx );
-			const uint32_t pix = __ldg( src + idx );
-			uint32_t o = (uint32_t)__ldg( cmap + (( pix >> 3 ) | (( light & 0x1f00u ) << 5 ))) | ( pix & 7u );
-			if( mip == 0 && pix == RC_TRANSPARENT_COLOR )
-				o = RC_TRANSPARENT_COLOR;
-			if( j & 1 ) packed[j >> 1] |= o << 16; else packed[j >> 1] = o;
-			light -= step;
-		}
-		uint16_t *out = dst + (size_t)y * bw + x;
-		if( RL == 8 ) *reinterpret_cast<uint4 *>( out ) = make_uint4( packed[0], packed[1], packed[2 % ( RL / 2 )], packed[3 % ( RL / 2 )] );
-		else if( RL == 4 ) *reinterpret_cast<uint2 *>( out ) = make_uint2( packed[0], packed[1 % ( RL / 2 )] );
-		else *reinterpret_cast<uint32_t *>( out ) = packed[0];
+		const uint32_t e = w.cache_units[u];
+		const int32_t slot = w.cache_flist[e >> 6], mip = slot & 3;
+		const rc_surface_t *sf = &sc.surfaces[slot >> 2];
+		const rc_texture_t *tex = &sc.textures[sf->texnum];
+		const int32_t smax = sf->lightextents[0] / sf->sample_size + 1;
+		const int32_t bw = sf->lightextents[0] >> mip, bh = sf->lightextents[1] >> mip, nbu = bw >> ( 4 - mip );
+		int32_t smaxt = tex->width >> mip;
+		if( smaxt < 1 ) smaxt = 1;
+		const int32_t lim = tex->width * tex->height * 2;
+		const uint16_t *src = sc.texels + tex->ofs[mip];
+		uint16_t *dst = sc.cache + sf->cache_ofs[mip];
+		const uint32_t *bl = w.cache_lux + (size_t)slot * CACHE_FLUX;
+		const int32_t *rc = w.cache_src + (size_t)slot * CACHE_FLUX;
+		const int32_t r = (int32_t)( e & 63u ) * 256 + threadIdx.x;
+		if( mip <= 1 ) { const int32_t rpr = bw / 8; if( r < rpr * bh ) rc_cache_run<8>( src, sc.colormap, lim, smaxt, mip, bl, smax, rc, nbu, dst, bw, rpr, r ); }
+		else if( mip == 2 ) { const int32_t rpr = bw / 4; if( r < rpr * bh ) rc_cache_run<4>( src, sc.colormap, lim, smaxt, mip, bl, smax, rc, nbu, dst, bw, rpr, r ); }
+		else { const int32_t rpr = bw / 2; if( r < rpr * bh ) rc_cache_run<2>( src, sc.colormap, lim, smaxt, mip, bl, smax, rc, nbu, dst, bw, rpr, r ); }
+	}
+}
+
+/* the keys of the blocks k_cache_texels wrote (after it, in stream order: a key says "these texels are current") */
+__global__ void __launch_bounds__( 256 ) k_cache_publish( rc_scene_t sc, rc_work_t w )
+{
+	const int32_t it = blockIdx.x * blockDim.x + threadIdx.x;
+	unsigned long long texels = 0;
+	if( it < w.cache_fn[0] )
+	{
+		const int32_t slot = w.cache_flist[it], mip = slot & 3;
+		const rc_surface_t *sf = &sc.surfaces[slot >> 2];
+		rc_cachekey_t *kk = &w.cache_keys[slot];
+		kk->texnum = sf->texnum;
+		for( int j = 0; j < RC_MAXLIGHTMAPS; j++ )
+			kk->light[j] = sf->styles[j] != 255 ? w.styles[sf->styles[j]] : 0;
+		kk->dlight = ( w.ndlights && w.dlightbits[slot >> 2] ) ? 1 : 0;
+		kk->valid = 1;
+		texels = (unsigned long long)( sf->lightextents[0] >> mip ) * ( sf->lightextents[1] >> mip );
+	}
+	/* batch counters: one atomic pair per warp */
+	const unsigned m = __activemask();
+	const unsigned long long tsum = __reduce_add_sync( m, (unsigned)texels );
+	const unsigned nb = __popc( __ballot_sync( m, texels != 0 ));
+	if(( threadIdx.x & 31 ) == __ffs( (int)m ) - 1 && nb )
+	{
+		atomicAdd( &w.counters[RC_CTR_CACHE_BLOCKS], (unsigned long long)nb );
+		atomicAdd( &w.counters[RC_CTR_CACHE_TEXELS], tsum );
 	}
 }
 
@@ -699,6 +845,7 @@ struct Dev
 	rc_cachekey_t *d_keys = nullptr;
 	uint32_t *d_need = nullptr;
 	int32_t *d_list = nullptr, *d_nlist = nullptr;
+	int32_t *d_flist = nullptr, *d_cachesrc = nullptr; uint32_t *d_units = nullptr, *d_cachelux = nullptr;
 	unsigned long long *d_counters = nullptr;
 
 	/* batch work buffers (grown on demand) */
@@ -978,6 +1125,9 @@ rc_work_t make_slice( int k, int v0, int v1 )
 	ws.cache_need = D.d_need + (size_t)k * ( nslots / 32 + 2 );
 	ws.cache_keys = D.d_keys;
 	ws.cache_list = D.d_list + (size_t)k * nslots;
+	ws.cache_flist = D.d_flist + (size_t)k * nslots; ws.cache_units = D.d_units + (size_t)k * nslots * 32;
+	ws.cache_lux = D.d_cachelux + (size_t)k * nslots * CACHE_FLUX; ws.cache_src = D.d_cachesrc + (size_t)k * nslots * CACHE_FLUX;
+	ws.cache_fn = D.d_nlist + 16 * k + 10;
 	ws.cache_nlist = D.d_nlist + 16 * k; ws.cache_cursor = ws.cache_nlist + 1; ws.line_cursor = ws.cache_nlist + 2; ws.heavy_count = ws.cache_nlist + 5; ws.wide_count = ws.cache_nlist + 6;
 	ws.heavy_list += (size_t)v0 * ws.height;
 	ws.wide_list += (size_t)v0 * ws.height;
@@ -1061,7 +1211,10 @@ int launch_slice( const rc_work_t &ws, int k, cudaStream_t st, cudaEvent_t *evs,
 		if( D.cache_aside ) CK( cudaStreamWaitEvent( aux, D.ev_cache[k][0], 0 ));
 		int nslots = sc.numsurfaces * 4;
 		k_cache_list<<<( nslots + 255 ) / 256, 256, 0, aux>>>( sc, ws ); D.launches++;
-		k_cache_build<<<148 * 4, CACHE_THREADS, 0, aux>>>( sc, ws ); D.launches++;
+		k_cache_light<<<148 * 4, 256, 0, aux>>>( sc, ws ); D.launches++;
+		k_cache_texels<<<148 * 8, 256, 0, aux>>>( sc, ws ); D.launches++;
+		k_cache_publish<<<( nslots + 255 ) / 256, 256, 0, aux>>>( sc, ws ); D.launches++;
+		k_cache_build<<<148 * 2, CACHE_THREADS, 0, aux>>>( sc, ws ); D.launches++; /* ragged blocks only: few or none */
 		KCHECK( "k_cache_list/build", aux );
 		CK( cudaEventRecord( D.ev_cache[k][1], aux ));
 	}
@@ -1300,7 +1453,7 @@ void rc_dev_shutdown( void )
 	/* everything rc_dev_init / the uploads created, so that R_Shutdown + R_Init (vid_restart) starts clean */
 	void **ptrs[] = { (void **)&D.d_leafkey, (void **)&D.d_tbord, (void **)&D.d_tbcounts, (void **)&D.d_tbsurfs, (void **)&D.d_tbedges, (void **)&D.d_bents, (void **)&D.d_bfaces, (void **)&D.d_leafbase, (void **)&D.d_viewbm, (void **)&D.d_bmvis, (void **)&D.d_pairs, (void **)&D.d_partbox, (void **)&D.d_itemvis, (void **)&D.d_cmds2d, (void **)&D.d_trikeys, (void **)&D.d_biglist, (void **)&D.d_sstatic, (void **)&D.d_parts, (void **)&D.d_bones, (void **)&D.d_blight, (void **)&D.d_mvpos, (void **)&D.d_mlight, (void **)&D.d_item_order, (void **)&D.d_polys, (void **)&D.d_alphamap, (void **)&D.d_addmap, (void **)&D.d_modmap, (void **)&D.d_items, (void **)&D.d_corners, (void **)&D.d_sortents, (void **)&D.d_display, (void **)&D.d_screenmap, (void **)&D.d_dlights, (void **)&D.d_dlightbits,
 		(void **)&D.d_colormap, (void **)&D.d_lightgamma, (void **)&D.d_sintable, (void **)&D.d_textures, (void **)&D.d_texels,
-		(void **)&D.d_styles, (void **)&D.d_keys, (void **)&D.d_need, (void **)&D.d_list, (void **)&D.d_nlist,
+		(void **)&D.d_styles, (void **)&D.d_keys, (void **)&D.d_need, (void **)&D.d_list, (void **)&D.d_nlist, (void **)&D.d_flist, (void **)&D.d_units, (void **)&D.d_cachelux, (void **)&D.d_cachesrc,
 		(void **)&D.d_counters, &D.d_flush };
 	for( void **p : ptrs ) { if( *p ) cudaFree( *p ); *p = nullptr; }
 	for( void *&p : D.d_scene ) { if( p ) cudaFree( p ); p = nullptr; }
@@ -1477,6 +1630,8 @@ int rc_dev_upload_scene( const rc_scene_t *sc, size_t cache_texels )
 	D.ndlights = 0;
 	if( upload( &D.d_need, (const uint32_t *)nullptr, RC_MAX_SLICES * ( nslots / 32 + 2 )) != 0 ) return -1;
 	if( upload( &D.d_list, (const int32_t *)nullptr, RC_MAX_SLICES * nslots ) != 0 ) return -1;
+	if( dalloc( &D.d_flist, (size_t)RC_MAX_SLICES * nslots ) != 0 || dalloc( &D.d_units, (size_t)RC_MAX_SLICES * nslots * 32 ) != 0 ) return -1;
+	if( dalloc( &D.d_cachelux, (size_t)RC_MAX_SLICES * nslots * CACHE_FLUX ) != 0 || dalloc( &D.d_cachesrc, (size_t)RC_MAX_SLICES * nslots * CACHE_FLUX ) != 0 ) return -1;
 	return 0;
 }
 

@@ -383,24 +383,16 @@ __global__ void __launch_bounds__( DR_WARPS * 32, 8 ) k_draw( rc_scene_t sc, rc_
 								s += A.z; t += A.w;
 							}
 						}
-						else if( kind2 == RC_KIND_SOLID && nmine == 4 )
-						{
-							/* the common case: a full quad from the surface cache, no predicates */
-							const uint16_t *blk = cache + (int32_t)B.z;
-#pragma unroll
-							for( int i = 0; i < 4; i++ )
-							{
-								col[i] = __ldg( blk + ( ((int32_t)s >> 16 ) + ((int32_t)t >> 16 ) * pitch ));
-								s += A.z; t += A.w;
-							}
-						}
 						else if( kind2 == RC_KIND_SOLID )
 						{
+							/* one path for full and partial quads (a span's last octet): two paths would both be walked by the
+							 * whole warp whenever a pass holds a span end - most passes do */
 							const uint16_t *blk = cache + (int32_t)B.z;
 #pragma unroll
 							for( int i = 0; i < 4; i++ )
 							{
-								col[i] = i < nmine ? (uint32_t)__ldg( blk + ( ((int32_t)s >> 16 ) + ((int32_t)t >> 16 ) * pitch )) : 0u;
+								const int32_t ti = ((int32_t)s >> 16 ) + ((int32_t)t >> 16 ) * pitch;
+								col[i] = (uint32_t)__ldg( blk + ( i < nmine ? ti : 0 ));
 								s += A.z; t += A.w;
 							}
 						}
@@ -443,6 +435,18 @@ __global__ void __launch_bounds__( DR_WARPS * 32, 8 ) k_draw( rc_scene_t sc, rc_
 							/* an aligned quad: one 8-byte store per plane */
 							*reinterpret_cast<uint2 *>( cp ) = make_uint2( col[0] | ( col[1] << 16 ), col[2] | ( col[3] << 16 ));
 							*reinterpret_cast<uint2 *>( zp ) = make_uint2( zv[0] | ( zv[1] << 16 ), zv[2] | ( zv[3] << 16 ));
+						}
+						else if( nmine == 4 && !(( x0 + i0 ) & 1 ) && !( w.width & 1 ))
+						{
+							/* an even start: two 4-byte stores per plane */
+							reinterpret_cast<uint32_t *>( cp )[0] = col[0] | ( col[1] << 16 ); reinterpret_cast<uint32_t *>( cp )[1] = col[2] | ( col[3] << 16 );
+							reinterpret_cast<uint32_t *>( zp )[0] = zv[0] | ( zv[1] << 16 ); reinterpret_cast<uint32_t *>( zp )[1] = zv[2] | ( zv[3] << 16 );
+						}
+						else if( nmine == 4 && !( w.width & 1 ))
+						{
+							/* an odd start: pixel, aligned pair, pixel */
+							cp[0] = (uint16_t)col[0]; *reinterpret_cast<uint32_t *>( cp + 1 ) = col[1] | ( col[2] << 16 ); cp[3] = (uint16_t)col[3];
+							zp[0] = (uint16_t)zv[0]; *reinterpret_cast<uint32_t *>( zp + 1 ) = zv[1] | ( zv[2] << 16 ); zp[3] = (uint16_t)zv[3];
 						}
 						else
 						{
