@@ -395,6 +395,14 @@ static void emu_draw_items( const rc_view_t *vw, const emu_viewctx_t &cx, uint16
 					const float *p = &E.mvpos[(size_t)( it->vert_base + m.vert ) * 3];
 					c[q].xyz[0] = p[0]; c[q].xyz[1] = p[1]; c[q].xyz[2] = p[2];
 					c[q].l = E.mlight[it->light_base + m.norm]; c[q].s = m.s; c[q].t = m.t;
+					if( it->chrome )
+					{
+						const rc_spart_t *pt = &E.parts[it->part];
+						int32_t cs, ct;
+						rc_studio_chrome_st( vw, E.bones.data() + (size_t)( pt->bones + E.sstatic[pt->snormbone + m.norm] ) * 12,
+							(const float *)E.sstatic.data() + pt->snorms + 3 * m.norm, it->skinwidth, it->skinheight, &cs, &ct );
+						c[q].s = (int16_t)cs; c[q].t = (int16_t)ct;
+					}
 				}
 				int k = rc_view_triangle( vw, &c[0], &c[1], &c[2], poly );
 				if( k ) emu_draw_poly( it, poly, k, color, zb, width );

@@ -650,3 +650,22 @@ def test_async_batches_match_synchronous_ones(pkg, scene):
     cc, cz = cu.render_views(sets[2])
     assert np.array_equal(col, want[1][0]) and np.array_equal(cc, want[2][0]) and np.array_equal(cz, want[2][1])
     assert all(v == 0 for k, v in cu.counters().items() if k.startswith("overflow"))
+
+
+def test_chrome_meshes_match_oracle(pkg, scene):
+    """STUDIO_NF_CHROME meshes on the device: the texel of a corner follows the viewer (rc_studio_chrome_st in the corner fetch
+    of k_tris_fast / k_tri_polys), 32 models in 48 views"""
+    import importlib
+    mdlgen = importlib.import_module("xash3d-fwgs_b200.tools.mdlgen")
+    mdl = mdlgen.generate(nbones=16, ring=24, texflags=0x0002, skin=64)
+    m = scene.make_map("small", ncameras=64)
+    cu = scene.Renderer(pkg.REF_CUDA_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    bare, _ = so.render_views(m.cameras[:48])
+    for r in (cu, so):
+        r.set_time(1.3)
+        scene.add_studio_models(r, m.cameras, 32, mdl=mdl)
+    cc, cz = cu.render_views(m.cameras[:48])
+    rc, rz = so.render_views(m.cameras[:48])
+    assert (rc != bare).mean() > 0.02
+    assert np.array_equal(cc, rc) and np.array_equal(cz, rz), ((cc == rc).mean(), (cz == rz).mean())

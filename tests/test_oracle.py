@@ -197,3 +197,25 @@ def test_scalar_translucent_brush_entities_match_oracle(pkg, scene):
     assert (rc != base).mean() > 0.05, "the oracle drew no translucent brush entities"
     assert np.array_equal(a, rc) and np.array_equal(az, rz)
     assert emu.counters()["overflow_bmodel"] == 0
+
+
+def test_scalar_chrome_meshes_match_oracle(pkg, scene):
+    """STUDIO_NF_CHROME meshes (R_StudioSetupChrome, R_StudioDrawChromeMesh): texture coordinates that follow the viewer,
+    rc_studio_chrome_st per (view, corner), through the CPU debug harness"""
+    import importlib
+    mdlgen = importlib.import_module("xash3d-fwgs_b200.tools.mdlgen")
+    mdl = mdlgen.generate(nbones=12, ring=16, texflags=0x0002, skin=64)
+    m = scene.make_map("small", ncameras=64)
+    emu = scene.Renderer(EMU_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    plain = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    for r in (emu, so):
+        r.set_time(1.0)
+        scene.add_studio_models(r, m.cameras, 16, mdl=mdl)
+    plain.set_time(1.0)
+    scene.add_studio_models(plain, m.cameras, 16, mdl=mdlgen.generate(nbones=12, ring=16, texflags=0, skin=64))
+    a, az = emu.render_views(m.cameras[:12])
+    rc, rz = so.render_views(m.cameras[:12])
+    p, _ = plain.render_views(m.cameras[:12])
+    assert not np.array_equal(p, rc), "the chrome flag changed nothing in the oracle"
+    assert np.array_equal(a, rc) and np.array_equal(az, rz)

@@ -1820,17 +1820,13 @@ static void rc_add_studio( cl_entity_t *e )
 		for( int jj = 0; jj < rs.sub[si].nmesh; jj++ )
 		{
 			const int j = order[jj];
-			if( FBitSet( rs.sub[si].mesh_flags[j], STUDIO_NF_CHROME ))
-			{
-				if( !rc.warned[5] ) { rc.warned[5] = true; gEngfuncs.Con_Reportf( "ref_cuda: chrome meshes are not drawn yet\n" ); }
-				continue;
-			}
 			GL_Bind( XASH_TEXTURE0, rs.sub[si].mesh_tex[j] );
 			rc_item_t *it = rc_new_item( RC_ITEM_MESH );
 			it->first = rs.sub[si].mesh_first[j];
 			it->count = rs.sub[si].mesh_ntris[j];
 			it->vert_base = pt->vert_base; it->light_base = pt->light_base;
 			it->part = (int)( pt - rs.parts );
+			it->chrome = FBitSet( rs.sub[si].mesh_flags[j], STUDIO_NF_CHROME ) ? 1 : 0;
 		}
 	}
 }

@@ -97,6 +97,14 @@ __device__ __forceinline__ int rc_item_corners( const rc_work_t &w, const rc_vie
 			const float *p = w.mvpos + (size_t)( it->vert_base + m.vert ) * 3;
 			c[q].xyz[0] = p[0]; c[q].xyz[1] = p[1]; c[q].xyz[2] = p[2];
 			c[q].l = w.mlight[it->light_base + m.norm]; c[q].s = m.s; c[q].t = m.t;
+			if( it->chrome )
+			{
+				const rc_spart_t *pt = &w.parts[it->part];
+				int32_t cs, ct;
+				rc_studio_chrome_st( vw, w.bones + (size_t)( pt->bones + w.sstatic[pt->snormbone + m.norm] ) * 12,
+					reinterpret_cast<const float *>( w.sstatic ) + pt->snorms + 3 * m.norm, it->skinwidth, it->skinheight, &cs, &ct );
+				c[q].s = (int16_t)cs; c[q].t = (int16_t)ct;
+			}
 		}
 		return 1;
 	}

@@ -200,7 +200,7 @@ typedef struct
 	/* RC_ITEM_MESH: the entity's slices of the batch's transformed vertices and per-normal lights */
 	int32_t vert_base, light_base;
 	int32_t part;                 /* RC_ITEM_MESH: index of its (entity, submodel) in the batch's part list; else -1 */
-	int32_t pad[1];
+	int32_t chrome;               /* RC_ITEM_MESH with STUDIO_NF_CHROME: texture coordinates per view from the normals (R_StudioSetupChrome) */
 } rc_item_t; /* 160 B */
 
 /* a studio submodel as the device keeps it (static per model file): R_StudioDrawPoints' inputs (ref/soft/r_studio.c:1802) */

@@ -569,6 +569,60 @@ RC_HD void rc_studio_vertex( const float *m, const float *v, float *out )
 	out[2] = v[0] * m[8] + v[1] * m[9] + v[2] * m[10] + m[11];
 }
 
+/* TriTexCoord2f (r_triapi.c:180): texture coordinate -> texel of the bound skin */
+RC_HD void rc_tri_texcoord( float u, float v, int32_t skinwidth, int32_t skinheight, int32_t *ps, int32_t *pt )
+{
+	double u1 = 0, v1 = 0;
+	u = fmodf( u, 10 );
+	v = fmodf( v, 10 );
+	if( u < 1000 && u > -1000 ) u1 = u;
+	if( v < 1000 && v > -1000 ) v1 = v;
+	while( u1 < 0 ) u1 = u1 + 1;
+	while( v1 < 0 ) v1 = v1 + 1;
+	while( u1 > 1 ) u1 = u1 - 1;
+	while( v1 > 1 ) v1 = v1 - 1;
+	u1 = u1 < 0.01 ? 0.01 : ( u1 > 0.99 ? 0.99 : u1 );
+	v1 = v1 < 0.01 ? 0.01 : ( v1 > 0.99 ? 0.99 : v1 );
+	*ps = (int32_t)( skinwidth * u1 );
+	*pt = (int32_t)( skinheight * v1 );
+}
+
+/* VectorNormalize (public/xash3d_mathlib.h:131): the length through the double-precision sqrt, rounded to float */
+RC_HD void rc_vec_normalize( float *v )
+{
+	float ilength = (float)sqrt( (double)rc_dot3( v, v ));
+	if( ilength ) ilength = 1.0f / ilength;
+	v[0] *= ilength; v[1] *= ilength; v[2] *= ilength;
+}
+
+/* R_StudioSetupChrome (r_studio.c:1169) + the coordinate R_StudioDrawChromeMesh hands to TriTexCoord2f (:1786): the texel a
+ * chrome mesh shows at a normal depends on where the viewer is - m: the normal's bone (matrix3x4), vw: the view
+ * (chrome_origin = vieworigin, r_studio.c:2318; RI.vright) */
+RC_HD void rc_studio_chrome_st( const rc_view_t *vw, const float *m, const float *normal, int32_t skinwidth, int32_t skinheight, int32_t *ps, int32_t *pt )
+{
+	float tmp[3], up[3], right[3], cup[3], cright[3];
+	tmp[0] = -vw->origin[0]; tmp[1] = -vw->origin[1]; tmp[2] = -vw->origin[2];
+	tmp[0] += m[3]; tmp[1] += m[7]; tmp[2] += m[11];
+	rc_vec_normalize( tmp );
+	/* CrossProduct( tmp, RI.vright, chromeupvec ) */
+	up[0] = tmp[1] * vw->vright[2] - tmp[2] * vw->vright[1];
+	up[1] = tmp[2] * vw->vright[0] - tmp[0] * vw->vright[2];
+	up[2] = tmp[0] * vw->vright[1] - tmp[1] * vw->vright[0];
+	rc_vec_normalize( up );
+	right[0] = up[1] * tmp[2] - up[2] * tmp[1];
+	right[1] = up[2] * tmp[0] - up[0] * tmp[2];
+	right[2] = up[0] * tmp[1] - up[1] * tmp[0];
+	rc_vec_normalize( right );
+	/* Matrix3x4_VectorIRotate */
+	for( int i = 0; i < 3; i++ )
+	{
+		cup[i] = up[0] * m[i] + up[1] * m[4 + i] + up[2] * m[8 + i];
+		cright[i] = right[0] * m[i] + right[1] * m[4 + i] + right[2] * m[8 + i];
+	}
+	const float cs = ( rc_dot3( normal, cright ) + 1.0f ) * 32.0f, ct = ( rc_dot3( normal, cup ) + 1.0f ) * 32.0f;
+	rc_tri_texcoord( cs * ( 1.0f / (float)skinwidth ), ct * ( 1.0f / (float)skinheight ), skinwidth, skinheight, ps, pt );
+}
+
 /* R_StudioLighting (r_studio.c:1391) for one normal, then what R_StudioSetColorBegin / TriColor4ub / _TriColor4f
  * (r_studio.c:1509, r_triapi.c:83-141) make of it: the light level (<< 8) every strip vertex with this normal gets */
 RC_HD int32_t rc_studio_light( const rc_spart_t *pt, int flags, const float *normal, const float *blightvec, const uint16_t *lightgamma )
