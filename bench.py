@@ -131,12 +131,12 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def measured_traffic(key="k_draw_dram_bytes_per_launch"):
-    """dram bytes per launch of a kernel from the committed ncu capture (profiles/traffic.json), if one exists."""
+def measured_traffic(config_id, key="k_draw_dram_bytes_per_launch"):
+    """dram bytes per launch of a kernel from the committed ncu capture of this workload (profiles/traffic.json), if one exists."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(p):
         try:
-            return json.load(open(p)).get(key)
+            return json.load(open(p)).get(config_id, {}).get(key)
         except Exception:
             return None
     return None
@@ -452,11 +452,11 @@ def run_cuda(args):
                                  "ms_per_step": e2e_z_s * 1e3, "note": "the same call with the z buffers copied out as well (what the reference arm leaves in host memory)"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": "k_draw", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": measured_traffic(), "algorithmic_bytes_per_launch": BYTES_PER_PIXEL * px, "peak_source": peak_src,
+                         "traffic": measured_traffic(args.config) if args.views == {"c2": 256, "c3": 8, "c4": 256, "c5": 4096}[args.config] else None, "algorithmic_bytes_per_launch": BYTES_PER_PIXEL * px, "peak_source": peak_src,
                          "kernel_ms": ms_scan},
             "roofline_surface_cache": {"bound": "hbm", "kernel": "k_cache_build (+ k_cache_list)", "achieved": 4 * cache_texels / (ms_cache * 1e-3) / 1e9,
                                        "peak": peak, "unit": "GB/s", "frac": 4 * cache_texels / (ms_cache * 1e-3) / 1e9 / peak,
-                                       "algorithmic_bytes_per_launch": 4 * cache_texels, "kernel_ms": ms_cache, "traffic": measured_traffic("k_cache_build_dram_bytes_per_launch"),
+                                       "algorithmic_bytes_per_launch": 4 * cache_texels, "kernel_ms": ms_cache, "traffic": measured_traffic(args.config, "k_cache_build_dram_bytes_per_launch"),
                                        "note": "forced rebuild of every (face, mip) block this rank's batch samples: 4 B per cache texel (2 B texel read + 2 B written), luxel bytes not counted"},
             "value_note": ("value is timed with EVERY surface-cache block the batch samples invalidated before each step (a superset of the blocks whose light styles changed)" if args.rebuild else None),
             "roofline_display_tail": {"bound": "hbm", "kernel": "k_blit<4> (pixel_t -> XRGB8888)", "achieved": 6 * px / (ms_blit * 1e-3) / 1e9, "peak": peak,
