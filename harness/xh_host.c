@@ -579,6 +579,13 @@ uint64_t xh_callback_count( void ) { return xh.callbacks; }
 /* ------------------------------------------------------------------ */
 /* time / light styles                                                   */
 
+/* the renderer's R_LightPoint slot at p -> r, g, b, a */
+void xh_light_point( const float *p, int *out )
+{
+	colorVec c = xh.ref.R_LightPoint( p );
+	out[0] = c.r; out[1] = c.g; out[2] = c.b; out[3] = c.a;
+}
+
 /* V_CheckGamma (engine/client/gamma.c:117-141): new tables, then the renderer is told */
 void xh_gamma_changed( float gamma, float brightness, float texgamma, float lightgamma )
 {

@@ -219,3 +219,13 @@ def test_scalar_chrome_meshes_match_oracle(pkg, scene):
     p, _ = plain.render_views(m.cameras[:12])
     assert not np.array_equal(p, rc), "the chrome flag changed nothing in the oracle"
     assert np.array_equal(a, rc) and np.array_equal(az, rz)
+
+
+def test_light_point_slot_matches_oracle(pkg, scene):
+    """the R_LightPoint slot (ref/common/ref_light.c:471) answers as ref_soft does at every camera position of the map"""
+    m = scene.make_map("small", ncameras=64)
+    emu = scene.Renderer(EMU_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    got = [emu.light_point(c[:3]) for c in m.cameras[:64]]
+    want = [so.light_point(c[:3]) for c in m.cameras[:64]]
+    assert got == want and len(set(want)) > 8

@@ -2420,7 +2420,15 @@ static qboolean VID_ScreenShot( const char *filename, int shot_type )
 	return result;
 }
 static qboolean VID_CubemapShot( const char *base, uint size, const float *vieworg, qboolean skyshot ) { (void)base; (void)size; (void)vieworg; (void)skyshot; return false; }
-static colorVec R_LightPoint( const float *p ) { colorVec c = { 255, 255, 255, 255 }; (void)p; return c; }
+/* R_LightPoint (ref/common/ref_light.c:471): the light the world throws on the ground below p */
+static colorVec R_LightPoint( const float *p )
+{
+	const vec3_t p0 = { p[0], p[1], p[2] }, p1 = { p[0], p[1], p[2] - 2048.0f };
+	uint light[3];
+	rc_light_vec( p0, p1, false, light );
+	colorVec c = { light[0], light[1], light[2], 255 };
+	return c;
+}
 static void R_DecalShoot( int textureIndex, int entityIndex, int modelIndex, vec3_t pos, int flags, float scale )
 { (void)textureIndex; (void)entityIndex; (void)modelIndex; (void)pos; (void)flags; (void)scale; }
 static void R_DecalRemoveAll( int texture ) { (void)texture; }

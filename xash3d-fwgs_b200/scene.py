@@ -81,6 +81,15 @@ class Renderer:
     def set_time(self, t):
         self.host.set_time(t)
 
+    def light_point(self, p):
+        """the renderer's R_LightPoint slot: light of the world on the ground below p -> (r, g, b)"""
+        L = self.host.lib
+        L.xh_light_point.argtypes = [C.c_void_p, C.c_void_p]
+        pp = (C.c_float * 3)(*[float(x) for x in p])
+        out = (C.c_int * 4)()
+        L.xh_light_point(pp, out)
+        return tuple(out[:3])
+
     def gamma_changed(self, gamma=2.5, brightness=0.0, texgamma=2.0, lightgamma=2.5):
         """the engine's V_CheckGamma: the four gamma tables rebuilt in place, then R_GammaChanged( false )"""
         L = self.host.lib
