@@ -256,7 +256,33 @@ const void *xh_sw_buffer( int *w, int *h, int *bpp )
 static void xh_SW_UnlockBuffer( void ) {}
 
 static void xh_R_StoreEfrags( struct efrag_s **pp, int framecount ) { (void)pp; (void)framecount; }
-static void xh_CL_DrawEFX( float time, qboolean trans ) { (void)time; (void)trans; xh.callbacks++; }
+/* the client's effects pass (CL_DrawEFX, engine/client/cl_efx.c:2079): the particles the test placed go to the renderer in the
+ * translucent pass, as the engine hands over cl_active_particles */
+static particle_t xh_particles[4096];
+static int xh_nparticles;
+static void xh_CL_ThinkParticle( double frametime, particle_t *p ) { (void)frametime; (void)p; }
+static void xh_CL_DrawEFX( float time, qboolean trans )
+{
+	xh.callbacks++;
+	if( trans && xh_nparticles && xh.ref.CL_DrawParticles )
+		xh.ref.CL_DrawParticles( time, xh_particles, 2.0f ); /* PART_SIZE = max( 0.5, cl_draw_particles ): 2 keeps them visible at 320x240 */
+}
+
+/* fp: n x {x, y, z, colour index, die time, type} */
+int xh_set_particles( const float *fp, int n )
+{
+	if( n > 4096 ) n = 4096;
+	memset( xh_particles, 0, sizeof( xh_particles ));
+	for( int i = 0; i < n; i++ )
+	{
+		particle_t *p = &xh_particles[i];
+		p->org[0] = fp[6 * i]; p->org[1] = fp[6 * i + 1]; p->org[2] = fp[6 * i + 2];
+		p->color = (short)fp[6 * i + 3]; p->die = fp[6 * i + 4]; p->type = (ptype_t)(int)fp[6 * i + 5];
+		p->next = i + 1 < n ? &xh_particles[i + 1] : NULL;
+	}
+	xh_nparticles = n;
+	return n;
+}
 static struct cl_entity_s *xh_R_BeamGetEntity( int i ) { (void)i; return NULL; }
 /* engine/common/model.c Mod_Extradata: the cache data of a model of the asked-for type only */
 static void *xh_Mod_Extradata( int type, model_t *m ) { return ( m && (int)m->type == type ) ? m->cache.data : NULL; }
@@ -385,6 +411,7 @@ static void xh_fill_engfuncs( ref_api_t *e )
 	e->Mod_BoxVisible = xh_Mod_BoxVisible;
 	e->Mod_PointInLeaf = xh_Mod_PointInLeaf;
 	e->CL_DrawEFX = xh_CL_DrawEFX;
+	e->CL_ThinkParticle = xh_CL_ThinkParticle;
 	e->R_StoreEfrags = xh_R_StoreEfrags;
 	e->Mod_Extradata = xh_Mod_Extradata;
 	e->CL_ExtraUpdate = xh_void;

@@ -77,6 +77,7 @@ XH_EXPORT int xh_load_pic( const char *name, int w, int h, const void *rgba, int
 XH_EXPORT int xh_frame_views_hud( const float *cams, int n, float fov_x, float fov_y, int x, int y, int w, int h, int flags,
 	const float *hud, int nhud, void *display_out );
 XH_EXPORT int xh_screenshot( int shot_type, void *out, size_t cap, int *width, int *height );
+XH_EXPORT int xh_set_particles( const float *fp, int n );
 XH_EXPORT void xh_light_point( const float *p, int *out );
 XH_EXPORT void xh_gamma_changed( float gamma, float brightness, float texgamma, float lightgamma );
 XH_EXPORT uint64_t xh_callback_count( void );            /* engine callbacks hit since init (debug) */

@@ -669,3 +669,19 @@ def test_chrome_meshes_match_oracle(pkg, scene):
     rc, rz = so.render_views(m.cameras[:48])
     assert (rc != bare).mean() > 0.02
     assert np.array_equal(cc, rc) and np.array_equal(cz, rz), ((cc == rc).mean(), (cz == rz).mean())
+
+
+def test_particles_match_oracle(pkg, scene):
+    """CL_DrawParticles on the device: 512 particles (RC_ITEM_PARTICLE, quads per view) with sprites in 32 views"""
+    m = scene.make_map("small", ncameras=64)
+    cu = scene.Renderer(pkg.REF_CUDA_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    bare, _ = so.render_views(m.cameras[:32])
+    for r in (cu, so):
+        r.set_time(1.0)
+        scene.add_particles(r, m.cameras[:32], 512, ahead=40.0)
+        add_test_sprites(r, m, m.cameras[:8], (2,))
+    cc, cz = cu.render_views(m.cameras[:32])
+    rc, rz = so.render_views(m.cameras[:32])
+    assert (rc != bare).mean() > 0.003
+    assert np.array_equal(cc, rc) and np.array_equal(cz, rz), ((cc == rc).mean(), (cz == rz).mean())

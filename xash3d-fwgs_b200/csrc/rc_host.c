@@ -100,6 +100,7 @@ static struct
 	/* view queue between R_BeginFrame and R_EndFrame */
 	rc_view_t   *views;
 	int          nviews, maxviews;
+	int          particleTexture; /* tr.particleTexture: the engine's "*particle" builtin, remembered by name (r_image.c:646) */
 	int          screen_view, screen_valid; /* the frame of the last batch R_EndFrame showed (VID_ScreenShot) */
 	rc_cmd2d_t  *cmds2d; int ncmds2d, maxcmds2d; /* the frame's HUD pass (R_DrawStretchPic / FillRGBA), applied in R_EndFrame */
 
@@ -325,7 +326,10 @@ static int GL_CreateTexture( const char *name, int width, int height, const void
 	pic.size = width * height * 4;
 	pic.flags = IMAGE_HAS_COLOR | ( FBitSet( flags, TF_HAS_ALPHA ) ? IMAGE_HAS_ALPHA : 0 );
 	pic.buffer = (byte *)buffer; /* only read: the texture keeps a copy */
-	return GL_LoadTextureFromBuffer( name, &pic, flags, false );
+	const int texnum = GL_LoadTextureFromBuffer( name, &pic, flags, false );
+	if( name && !strcmp( name, REF_PARTICLE_TEXTURE ))
+		rc.particleTexture = texnum;
+	return texnum;
 }
 
 static int GL_FindTexture( const char *name )
@@ -2477,7 +2481,36 @@ static void Mod_StudioLoadTextures( model_t *mod, void *data )
 			tx->index = GL_FindTexture( REF_DEFAULT_TEXTURE );
 	}
 }
-static void CL_DrawParticles( double frametime, particle_t *particles, float partsize ) { (void)frametime; (void)particles; (void)partsize; }
+/* CL_DrawParticles (ref/soft/r_part.c:47): every live particle becomes a draw item; its quad is built per view on the device
+ * (rc_particle_corners).  Colour from the engine's palette, faded over the last 1/16 s of the particle's life. */
+static void CL_DrawParticles( double frametime, particle_t *particles, float partsize )
+{
+	if( !particles )
+		return;
+	const color24 *palette = (const color24 *)gEngfuncs.EngineGetParm( PARM_GET_PALETTE_PTR, 0 );
+	GL_SetRenderMode( kRenderTransAdd );
+	GL_Bind( XASH_TEXTURE0, rc.particleTexture );
+	for( particle_t *p = particles; p; p = p->next )
+	{
+		if(( p->type != pt_blob ) || ( p->unused == 255 ))
+		{
+			p->color = bound( 0, p->color, 255 );
+			const color24 color = palette ? palette[p->color] : (color24){ 255, 255, 255 };
+			int alpha = 255 * ( p->die - gp_cl->time ) * 16.0f;
+			if( alpha > 255 || p->type == pt_static )
+				alpha = 255;
+			rc_tri_color4f( 1.0f * alpha / 255 / 255 * color.r, 1.0f * alpha / 255 / 255 * color.g, 1.0f * alpha / 255 / 255 * color.b, 1.0f );
+			rc_item_t *it = rc_new_item( RC_ITEM_PARTICLE );
+			it->count = 2;
+			it->light = (int32_t)( rc.tri.light << 8 );
+			it->scale = partsize;
+			VectorCopy( p->org, it->origin );
+			TriTexCoord2f( 0.0f, 0.0f ); it->s0 = rc.tri.s; it->t0 = rc.tri.t;
+			TriTexCoord2f( 1.0f, 1.0f ); it->s1 = rc.tri.s; it->t1 = rc.tri.t;
+		}
+		gEngfuncs.CL_ThinkParticle( frametime, p );
+	}
+}
 static void CL_DrawTracers( double frametime, particle_t *tracers ) { (void)frametime; (void)tracers; }
 static void CL_DrawBeams( int fTrans, BEAM *beams ) { (void)fTrans; (void)beams; }
 

@@ -167,7 +167,8 @@ typedef struct
  * turns the frame's entity lists into an ordered list of draw items - the order R_DrawEntitiesOnList (r_main.c:504)
  * draws in; translucent entities come with a sort record, their order is per view (R_TransEntityCompare, r_main.c:157).
  */
-enum { RC_ITEM_TRIS = 0, RC_ITEM_SPRITE = 1, RC_ITEM_MESH = 2, RC_ITEM_BRUSH = 3 /* a translucent brush entity: first = its rc_bent_t */ };
+enum { RC_ITEM_TRIS = 0, RC_ITEM_SPRITE = 1, RC_ITEM_MESH = 2, RC_ITEM_BRUSH = 3 /* a translucent brush entity: first = its rc_bent_t */,
+	RC_ITEM_PARTICLE = 4 /* a particle of CL_DrawParticles: a quad that faces every view (origin, scale = partsize) */ };
 /* the span drawer a texture bind selects (GL_Bind, ref/soft/r_image.c:43-75): R_PolysetFillSpans8, ...Additive, ...Glow,
  * ...TextureBlended, ...Blended (r_polyse.c:724-1214) */
 enum { RC_DRAW_FILL = 0, RC_DRAW_ADDITIVE = 1, RC_DRAW_GLOW = 2, RC_DRAW_TEXBLEND = 3, RC_DRAW_BLEND = 4 };

@@ -727,6 +727,32 @@ RC_HD int rc_sprite_corners( const rc_view_t *vw, const rc_item_t *it, rc_corner
 	return 1;
 }
 
+/* CL_DrawParticles (ref/soft/r_part.c:47): the quad of one particle for a view - it faces the view (cull_vright / cull_vup) and
+ * grows with the distance along the view direction so that it does not vanish; corners in TriVertex3f order */
+RC_HD int rc_particle_corners( const rc_view_t *vw, const rc_item_t *it, rc_corner_t *q )
+{
+	const float partsize = it->scale;
+	float size = partsize;
+	size += ( it->origin[0] - vw->origin[0] ) * vw->vforward[0];
+	size += ( it->origin[1] - vw->origin[1] ) * vw->vforward[1];
+	size += ( it->origin[2] - vw->origin[2] ) * vw->vforward[2];
+	if( size < 20.0f ) size = partsize;
+	else size = partsize + size * 0.002f;
+	float right[3], up[3];
+	for( int k = 0; k < 3; k++ ) { right[k] = vw->vright[k] * size; up[k] = vw->vup[k] * size; }
+	for( int k = 0; k < 3; k++ )
+	{
+		q[0].xyz[k] = it->origin[k] - right[k] + up[k];
+		q[1].xyz[k] = it->origin[k] + right[k] + up[k];
+		q[2].xyz[k] = it->origin[k] + right[k] - up[k];
+		q[3].xyz[k] = it->origin[k] - right[k] - up[k];
+	}
+	/* TriTexCoord2f( 0, 1 ), ( 0, 0 ), ( 1, 0 ), ( 1, 1 ) */
+	q[0].s = it->s0; q[0].t = it->t1; q[1].s = it->s0; q[1].t = it->t0; q[2].s = it->s1; q[2].t = it->t0; q[3].s = it->s1; q[3].t = it->t1;
+	for( int k = 0; k < 4; k++ ) q[k].l = it->light;
+	return 1;
+}
+
 /*
  * One triangle of a draw item for one view, as the reference draws it: corners -> R_SetupFinalVert ->
  * R_RenderTriangle (trivial reject, R_AliasClipTriangle).  poly receives the vertices of the polygon to draw (3 when

@@ -81,6 +81,14 @@ class Renderer:
     def set_time(self, t):
         self.host.set_time(t)
 
+    def set_particles(self, parts):
+        """the client's active particles: rows of {x, y, z, palette index, die time, ptype_t}; drawn by CL_DrawParticles in every
+        following batch (needs a texture named '*particle': load_pic)"""
+        a = np.ascontiguousarray(np.asarray(parts, dtype=np.float32).reshape(-1, 6))
+        L = self.host.lib
+        L.xh_set_particles.argtypes = [C.c_void_p, C.c_int]
+        return L.xh_set_particles(a.ctypes.data, len(a))
+
     def light_point(self, p):
         """the renderer's R_LightPoint slot: light of the world on the ground below p -> (r, g, b)"""
         L = self.host.lib
@@ -358,6 +366,27 @@ def add_mixed_brush_entities(r, m, cams):
     add_brush_entities(r, m, cams[8:], 6, rotate=True, rendermode=2, renderamt=140)
     add_brush_entities(r, m, cams[14:], 6, rotate=False, rendermode=5, renderamt=200)
     add_brush_entities(r, m, cams[20:], 6, rotate=True, rendermode=4, renderamt=255)
+
+
+def add_particles(r, cams, count=256, ahead=60.0, seed=5):
+    """`count` particles scattered in front of the cameras (palette colours, some fading out): CL_DrawParticles' input"""
+    rng = np.random.default_rng(seed)
+    d = np.zeros((8, 8, 4), np.uint8)
+    yy, xx = np.mgrid[0:8, 0:8]
+    dot = np.clip(255 - 60 * np.hypot(xx - 3.5, yy - 3.5), 0, 255).astype(np.uint8)
+    d[..., 0] = d[..., 1] = d[..., 2] = dot
+    d[..., 3] = 255
+    r.load_pic("*particle", d)
+    cams = np.asarray(cams, dtype=np.float32).reshape(-1, 6)
+    rows = []
+    for k in range(count):
+        c = cams[k % len(cams)]
+        yaw = math.radians(float(c[4]))
+        off = rng.uniform(-24, 24, 3)
+        dist = ahead + 10.0 * (k // len(cams))
+        rows.append([c[0] + dist * math.cos(yaw) + off[0], c[1] + dist * math.sin(yaw) + off[1], c[2] + off[2] * 0.5,
+                     int(rng.integers(40, 256)), 1.0 + [10.0, 0.03, 0.05][k % 3], [0, 0, 6][k % 3]])  # pt_static, pt_static fading, pt_fire
+    return r.set_particles(rows)
 
 
 def sprite_image(seed, w=64, h=64):
