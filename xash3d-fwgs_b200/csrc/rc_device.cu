@@ -858,6 +858,7 @@ struct Dev
 	struct batch_graph_t { cudaGraphExec_t exec = nullptr; unsigned long long key = 0, launches = 0; };
 	batch_graph_t graphs[4][2]; /* [segment][frame buffer set] */
 	bool use_graphs = true;
+	int tr_strips = TR_STRIPS; /* horizontal strips of a frame in k_tris_ordered (RC_TR_STRIPS: measurement only) */
 	cudaEvent_t ev_join[2] = {};
 	std::vector<rc_view_t> pend_views; int pend_w = 0, pend_h = 0, pend_clear = 0; uint16_t *pend_color = nullptr; int16_t *pend_z = nullptr;
 	/* per-view capacities: they start from what a view typically needs and follow the counters of the batches
@@ -1266,7 +1267,7 @@ int launch_slice( const rc_work_t &ws, int k, cudaStream_t st, cudaEvent_t *evs,
 					dim3 gp(( nord + 127 ) / 128, ws.nviews );
 					k_tri_polys<<<gp, 128, 0, st>>>( ws, nord ); D.launches++;
 				}
-				dim3 gt( ws.nviews, TR_STRIPS );
+				dim3 gt( ws.nviews, D.tr_strips );
 				k_tris_ordered<<<gt, TR_THREADS, 0, st>>>( sc, ws, nord ); D.launches++;
 			}
 			KCHECK( "k_tris", st );
@@ -1429,6 +1430,7 @@ int rc_dev_init( int device )
 	CK( cudaEventCreateWithFlags( &D.ev_fork, cudaEventDisableTiming ));
 	for( auto &e : D.ev_join ) CK( cudaEventCreateWithFlags( &e, cudaEventDisableTiming ));
 	D.use_graphs = getenv( "RC_NO_GRAPHS" ) == nullptr;
+	if( const char *e = getenv( "RC_TR_STRIPS" )) { const int n = atoi( e ); if( n >= 1 && n <= 64 ) D.tr_strips = n; }
 	for( auto &ss : D.slice_stream ) CK( cudaStreamCreateWithFlags( &ss, cudaStreamNonBlocking ));
 	for( auto &ss : D.aux_stream ) CK( cudaStreamCreateWithFlags( &ss, cudaStreamNonBlocking ));
 	for( auto &e : D.ev_cache ) { CK( cudaEventCreate( &e[0] )); CK( cudaEventCreate( &e[1] )); }

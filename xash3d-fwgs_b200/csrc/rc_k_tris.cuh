@@ -11,9 +11,12 @@
  *                 the screen-space polygon the reference would fan into triangles, left in HBM.
  *   k_tris_ordered  the span drawers read and write the frame, and all but the opaque one blend: triangles have to
  *                 reach a pixel in submission order.  Block per (view, horizontal strip of the frame): it walks the
- *                 view's triangles in order; per triangle one thread sets up the edge walk (rc_tri_setup), then the
- *                 block's warps take the scanlines inside the strip, lanes the pixels of a scanline - every scanline and
- *                 pixel is closed form (rc_tri_row), so the result is the reference's sequential one.
+ *                 view's items in order, 128 at a time; between two translucent brush entities the items' polygons are
+ *                 one flat list.  Thread = polygon: the fan triangles whose scanlines reach into the strip, compacted
+ *                 in order (block prefix sum); the others cost nothing more.  Those are set up
+ *                 TR_BATCH at a time (thread = triangle, rc_tri_setup), then drawn one after the other: thread =
+ *                 scanline (closed form, rc_tri_row), a prefix sum over the scanlines' pixel counts, thread = pixel.
+ *                 Every scanline and pixel is closed form, so the result is the reference's sequential one.
  */
 #ifndef RC_K_TRIS_CUH
 #define RC_K_TRIS_CUH
@@ -257,6 +260,12 @@ __global__ void __launch_bounds__( 128 ) k_tri_polys( rc_work_t w, int32_t ntris
 		out->v[i][0] = poly[i].u; out->v[i][1] = poly[i].v; out->v[i][2] = poly[i].s;
 		out->v[i][3] = poly[i].t; out->v[i][4] = poly[i].l; out->v[i][5] = poly[i].zi;
 	}
+	/* RC_CTR_TRIS: the fan triangles R_DrawTriangle accepts (k_tris_ordered sets up only those that reach into a strip) */
+	int32_t ndrawn = 0;
+	rc_trisetup_t ts;
+	for( int i = 1; i < k - 1; i++ )
+		ndrawn += rc_tri_setup( &poly[0], &poly[i], &poly[i + 1], it->skinwidth, it->skinheight, &ts );
+	if( ndrawn ) atomicAdd( &w.counters[RC_CTR_TRIS], (unsigned long long)ndrawn );
 }
 
 /*
@@ -327,12 +336,45 @@ __device__ __forceinline__ void rc_tbrush_draw( const rc_scene_t &sc, const rc_w
 	}
 }
 
+#define TR_BATCH 16 /* triangles of a strip set up side by side before they are drawn one after the other */
+
+/* block-wide exclusive prefix sum of one value per thread; *total = the sum.  Two barriers. */
+__device__ __forceinline__ int32_t rc_block_excl_scan( int32_t v, int32_t *wsum, int t, int32_t *total )
+{
+	const int lane = t & 31, warp = t >> 5;
+	const int32_t incl = rc_warp_incl_scan( v, lane );
+	__syncthreads(); /* wsum of the previous scan has been read */
+	if( lane == 31 ) wsum[warp] = incl;
+	__syncthreads();
+	int32_t wbase = 0, sum = 0;
+#pragma unroll
+	for( int k = 0; k < TR_THREADS / 32; k++ ) { if( k < warp ) wbase += wsum[k]; sum += wsum[k]; }
+	*total = sum;
+	return wbase + incl - v;
+}
+
 __global__ void __launch_bounds__( TR_THREADS ) k_tris_ordered( rc_scene_t sc, rc_work_t w, int32_t ntris )
 {
-	__shared__ rc_trisetup_t s_ts;
-	__shared__ int32_t s_go, s_y0, s_rows;
-	__shared__ rc_span_t s_tbspans[TR_THREADS / 32][32 * RC_TB_LINESPANS];
-	__shared__ int32_t s_tbn[TR_THREADS / 32][32];
+	/* a translucent brush entity's scanline spans and a batch of triangle set-ups are never live together */
+	union tr_shared_t
+	{
+		struct { rc_span_t spans[TR_THREADS / 32][32 * RC_TB_LINESPANS]; int32_t n[TR_THREADS / 32][32]; } tb;
+		struct
+		{
+			rc_trisetup_t ts[TR_BATCH];
+			int32_t y0[TR_BATCH], rows[TR_BATCH];
+			int4 item[TR_BATCH];               /* tex_ofs, drawer, color, alpha of the triangle's item */
+			rc_trirow_t row[TR_THREADS];
+			int32_t pre[TR_THREADS + 1];
+			uint32_t hit[TR_THREADS * 6];      /* polygon * 8 + fan triangle, in drawing order */
+			uint8_t hslot[TR_THREADS * 6];     /* its item's slot in the chunk */
+		} tr;
+	};
+	__shared__ tr_shared_t S;
+	__shared__ int32_t s_wsum[TR_THREADS / 32];
+	/* a chunk of the view's ordered items: item, first polygon (prefix sum of the triangle counts), polygon base */
+	__shared__ int32_t s_iidx[TR_THREADS], s_ipre[TR_THREADS + 1], s_ibase[TR_THREADS];
+	__shared__ uint32_t s_brush[TR_THREADS / 32];
 	const int view = blockIdx.x, strip = blockIdx.y, t = threadIdx.x, lane = t & 31, warp = t >> 5;
 	const int32_t ys0 = (int32_t)((long long)w.height * strip / gridDim.y ), ys1 = (int32_t)((long long)w.height * ( strip + 1 ) / gridDim.y );
 	uint16_t *color = w.color + (size_t)view * w.width * w.height;
@@ -341,75 +383,173 @@ __global__ void __launch_bounds__( TR_THREADS ) k_tris_ordered( rc_scene_t sc, r
 	const rc_poly_t *polys = w.polys + (size_t)view * ntris;
 	rc_blendluts_t L;
 	L.colormap = sc.colormap; L.alphamap = w.alphamap; L.addmap = w.addmap; L.modmap = w.modmap;
-	unsigned long long npix = 0, ndrawn = 0;
+	unsigned long long npix = 0;
 
-	for( int32_t oi = 0; oi < w.nitems; oi++ )
+	for( int32_t oc = 0; oc < w.nitems; oc += TR_THREADS )
 	{
-		const int32_t idx = order[oi];
-		if( idx < 0 )
-			break;
-		const rc_item_t *it = &w.items[idx];
-		if( it->tex_ofs < 0 || idx < w.nfast_items )
-			continue;
-		if( it->kind == RC_ITEM_BRUSH )
+		/* thread = item of the chunk (the list ends with -1s) */
+		const int32_t oi = oc + t;
+		const int32_t idx = oi < w.nitems ? order[oi] : -1;
+		int32_t cnt = 0, pbase = 0;
+		bool brush = false;
+		if( idx >= w.nfast_items )
 		{
-			__syncthreads(); /* the previous item's pixels are in the frame */
-			rc_tbrush_draw( sc, w, &L, view, it->first, ys0, ys1, color, zb, s_tbspans[warp], s_tbn[warp], lane, warp );
-			continue;
-		}
-		const uint16_t *skin = sc.texels + it->tex_ofs;
-		const int32_t drawer = it->drawer;
-		const uint32_t icolor = (uint32_t)it->color, ialpha = (uint32_t)it->alpha;
-		for( int32_t tri = 0; tri < it->count; tri++ )
-		{
-			const rc_poly_t *pl = &polys[it->order0 - w.fast_tris + tri];
-			const int32_t k = pl->k;
-			for( int32_t i = 1; i < k - 1; i++ )
+			const rc_item_t *it = &w.items[idx];
+			if( it->tex_ofs >= 0 )
 			{
-				__syncthreads(); /* the previous triangle's pixels are in the frame; s_ts is free */
-				if( t == 0 )
-				{
-					rc_fv_t a, b, c;
-					const int32_t *pa = pl->v[0], *pb = pl->v[i], *pc = pl->v[i + 1];
-					a.u = pa[0]; a.v = pa[1]; a.s = pa[2]; a.t = pa[3]; a.l = pa[4]; a.zi = pa[5];
-					b.u = pb[0]; b.v = pb[1]; b.s = pb[2]; b.t = pb[3]; b.l = pb[4]; b.zi = pb[5];
-					c.u = pc[0]; c.v = pc[1]; c.s = pc[2]; c.t = pc[3]; c.l = pc[4]; c.zi = pc[5];
-					int go = rc_tri_setup( &a, &b, &c, it->skinwidth, it->skinheight, &s_ts );
-					int32_t y0 = 0, rows = 0;
-					if( go )
-					{
-						rows = rc_tri_rows( &s_ts, &y0 );
-						if( strip == 0 ) ndrawn++;
-						go = y0 < ys1 && y0 + rows > ys0;
-					}
-					s_go = go; s_y0 = y0; s_rows = rows;
-				}
-				__syncthreads();
-				if( !s_go )
-					continue;
-				const int32_t y0 = s_y0;
-				const int32_t rlo = ys0 > y0 ? ys0 - y0 : 0, rhi = min( s_rows, ys1 - y0 );
-				for( int32_t r = rlo + warp; r < rhi; r += TR_THREADS / 32 )
-				{
-					rc_trirow_t row;
-					rc_tri_row( &s_ts, r, &row );
-					if( row.count <= 0 || !rc_tri_row_inbounds( &s_ts, &row ))
-						continue;
-					const size_t base = (size_t)( y0 + r ) * w.width + row.x;
-					for( int32_t p = lane; p < row.count; p += 32 )
-					{
-						const uint32_t src = __ldg( skin + rc_tri_texel( &s_ts, &row, p ));
-						const int32_t light = (int32_t)((uint32_t)row.l + (uint32_t)p * (uint32_t)s_ts.lstepx );
-						const int32_t zi = (int32_t)((uint32_t)row.zi + (uint32_t)p * (uint32_t)s_ts.zistepx );
-						rc_tri_shade( &L, drawer, icolor, ialpha, src, light, zi, &color[base + p], &zb[base + p] );
-					}
-					if( lane == 0 ) npix += (unsigned long long)row.count;
-				}
+				if( it->kind == RC_ITEM_BRUSH ) brush = true;
+				else if( w.itemvis[(size_t)view * w.nitems + idx] ) { cnt = it->count; pbase = it->order0 - w.fast_tris; }
 			}
 		}
+		int32_t npolys;
+		const int32_t ipre = rc_block_excl_scan( cnt, s_wsum, t, &npolys ); /* its first barrier: the previous chunk is done */
+		s_iidx[t] = idx; s_ipre[t] = ipre; s_ibase[t] = pbase;
+		if( t == 0 ) s_ipre[TR_THREADS] = npolys;
+		const uint32_t bm = __ballot_sync( 0xFFFFFFFFu, brush );
+		if( lane == 0 ) s_brush[warp] = bm;
+		if( __syncthreads_and( idx < 0 )) /* nothing but the list's tail */
+			break;
+
+		/* runs of items between translucent brush entities: the run's polygons, flat */
+		for( int32_t ra = 0; ra < TR_THREADS; )
+		{
+			int32_t rb_ = TR_THREADS;
+			for( int32_t wq = ra >> 5; wq < TR_THREADS / 32; wq++ )
+			{
+				uint32_t m = s_brush[wq];
+				if( wq == ( ra >> 5 )) m &= 0xFFFFFFFFu << ( ra & 31 );
+				if( m ) { rb_ = wq * 32 + __ffs( m ) - 1; break; }
+			}
+			const int32_t q0 = s_ipre[ra], q1 = s_ipre[rb_];
+			for( int32_t qb = q0; qb < q1; qb += TR_THREADS )
+			{
+				/* thread = polygon: which of its fan triangles reach into the strip (the scanlines a triangle covers are
+				 * [lowest v, highest v) of its corners: rc_tri_rows) */
+				uint32_t hm = 0;
+				int32_t slot = 0, pabs = 0;
+				if( qb + t < q1 )
+				{
+					const int32_t q = qb + t;
+					int32_t lo = ra, hi = rb_ - 1;
+					while( lo < hi )
+					{
+						const int32_t mid = ( lo + hi + 1 ) >> 1;
+						if( s_ipre[mid] <= q ) lo = mid; else hi = mid - 1;
+					}
+					slot = lo;
+					pabs = s_ibase[slot] + ( q - s_ipre[slot] );
+					const rc_poly_t *pl = &polys[pabs];
+					const int32_t k = pl->k;
+					if( k >= 3 )
+					{
+						const int32_t v0 = pl->v[0][1];
+						int32_t va = pl->v[1][1];
+						for( int32_t i = 1; i < k - 1; i++ )
+						{
+							const int32_t vb = pl->v[i + 1][1];
+							const int32_t vlo = min( v0, min( va, vb )), vhi = max( v0, max( va, vb ));
+							if( vlo < ys1 && vhi > ys0 ) hm |= 1u << i;
+							va = vb;
+						}
+					}
+				}
+				int32_t nhit;
+				int32_t at = rc_block_excl_scan( __popc( hm ), s_wsum, t, &nhit );
+				if( nhit == 0 )
+					continue;
+				for( uint32_t m = hm; m; m &= m - 1, at++ )
+				{
+					S.tr.hit[at] = ((uint32_t)pabs << 3 ) | (uint32_t)( __ffs( m ) - 1 );
+					S.tr.hslot[at] = (uint8_t)slot;
+				}
+				for( int32_t hb = 0; hb < nhit; hb += TR_BATCH )
+				{
+					__syncthreads(); /* the hit list is written; the previous batch's set-ups are free */
+					const int32_t nb = min( TR_BATCH, nhit - hb );
+					/* thread = triangle of the batch: the edge walk set-up (spread over the warps) */
+					const int32_t bj = lane * ( TR_THREADS / 32 ) + warp;
+					if( lane < TR_BATCH / ( TR_THREADS / 32 ) && bj < nb )
+					{
+						const uint32_t h = S.tr.hit[hb + bj];
+						const rc_item_t *it = &w.items[s_iidx[S.tr.hslot[hb + bj]]];
+						const rc_poly_t *pl = &polys[h >> 3];
+						const int32_t i = (int32_t)( h & 7 );
+						rc_fv_t a, b, c;
+						const int32_t *pa = pl->v[0], *pb = pl->v[i], *pc = pl->v[i + 1];
+						a.u = pa[0]; a.v = pa[1]; a.s = pa[2]; a.t = pa[3]; a.l = pa[4]; a.zi = pa[5];
+						b.u = pb[0]; b.v = pb[1]; b.s = pb[2]; b.t = pb[3]; b.l = pb[4]; b.zi = pb[5];
+						c.u = pc[0]; c.v = pc[1]; c.s = pc[2]; c.t = pc[3]; c.l = pc[4]; c.zi = pc[5];
+						int32_t y0 = 0, rows = 0;
+						if( rc_tri_setup( &a, &b, &c, it->skinwidth, it->skinheight, &S.tr.ts[bj] ))
+							rows = rc_tri_rows( &S.tr.ts[bj], &y0 );
+						S.tr.y0[bj] = y0; S.tr.rows[bj] = rows;
+						S.tr.item[bj] = make_int4( it->tex_ofs, it->drawer, it->color, it->alpha );
+					}
+					__syncthreads();
+					for( int32_t j = 0; j < nb; j++ )
+					{
+						const int32_t y0 = S.tr.y0[j];
+						const int32_t rlo = ys0 > y0 ? ys0 - y0 : 0, rhi = min( S.tr.rows[j], ys1 - y0 );
+						if( rlo >= rhi )
+							continue;
+						const rc_trisetup_t *ts = &S.tr.ts[j];
+						const int4 iv = S.tr.item[j];
+						const uint16_t *skin = sc.texels + iv.x;
+						/* the triangle's pixels inside the strip, flat over the block: thread = scanline sets the rows up
+						 * (closed form), a block prefix sum numbers the pixels, then thread = pixel.  A triangle writes a
+						 * pixel once. */
+						for( int32_t rb = rlo; rb < rhi; rb += TR_THREADS )
+						{
+							rc_trirow_t row;
+							int32_t pc = 0;
+							if( rb + t < rhi )
+							{
+								rc_tri_row( ts, rb + t, &row );
+								if( row.count > 0 && rc_tri_row_inbounds( ts, &row ))
+									pc = row.count;
+							}
+							int32_t total;
+							const int32_t pre = rc_block_excl_scan( pc, s_wsum, t, &total ); /* its first barrier: the previous triangle's pixels are in the frame */
+							if( total == 0 )
+								continue;
+							S.tr.row[t] = row;
+							S.tr.pre[t] = pre;
+							if( t == 0 ) S.tr.pre[TR_THREADS] = total;
+							__syncthreads();
+							for( int32_t p = t; p < total; p += TR_THREADS )
+							{
+								/* the row whose pixel range holds p */
+								int32_t lo = 0, hi = TR_THREADS - 1;
+								while( lo < hi )
+								{
+									const int32_t mid = ( lo + hi + 1 ) >> 1;
+									if( S.tr.pre[mid] <= p ) lo = mid; else hi = mid - 1;
+								}
+								const rc_trirow_t &rw = S.tr.row[lo];
+								const int32_t px = p - S.tr.pre[lo];
+								const size_t at2 = (size_t)( y0 + rb + lo ) * w.width + rw.x + px;
+								const uint32_t src = __ldg( skin + rc_tri_texel( ts, &rw, px ));
+								const int32_t light = (int32_t)((uint32_t)rw.l + (uint32_t)px * (uint32_t)ts->lstepx );
+								const int32_t zi = (int32_t)((uint32_t)rw.zi + (uint32_t)px * (uint32_t)ts->zistepx );
+								rc_tri_shade( &L, iv.y, (uint32_t)iv.z, (uint32_t)iv.w, src, light, zi, &color[at2], &zb[at2] );
+							}
+							if( t == 0 ) npix += (unsigned long long)total;
+							__syncthreads(); /* the rows are free; the pixels are in the frame */
+						}
+					}
+				}
+				__syncthreads(); /* the hit list is free */
+			}
+			if( rb_ < TR_THREADS )
+			{
+				__syncthreads(); /* the run's pixels are in the frame */
+				rc_tbrush_draw( sc, w, &L, view, w.items[s_iidx[rb_]].first, ys0, ys1, color, zb, S.tb.spans[warp], S.tb.n[warp], lane, warp );
+				__syncthreads();
+			}
+			ra = rb_ + 1;
+		}
 	}
-	if( lane == 0 && npix ) atomicAdd( &w.counters[RC_CTR_TRI_PIXELS], npix );
-	if( t == 0 && ndrawn ) atomicAdd( &w.counters[RC_CTR_TRIS], ndrawn );
+	if( t == 0 && npix ) atomicAdd( &w.counters[RC_CTR_TRI_PIXELS], npix );
 }
 
 /* ---------------------------------------------------------------------------------------------- */
