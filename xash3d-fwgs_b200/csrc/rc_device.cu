@@ -136,6 +136,7 @@ __device__ __forceinline__ int32_t rc_warp_incl_scan( int32_t x, int lane )
 /* ---------------------------------------------------------------------------------------------- */
 /* S0: visibility + BSP walk                                                                         */
 
+#include "rc_bulk.cuh"
 #include "rc_k_vis.cuh"
 
 /* ---------------------------------------------------------------------------------------------- */

@@ -52,31 +52,8 @@ static inline size_t rc_vis_tree_bytes( const rc_scene_t *sc )
 	return sizeof( rc_node_t ) * (size_t)sc->numnodes + sizeof( rc_plane_t ) * (size_t)sc->numplanes + sizeof( rc_leaf_t ) * (size_t)sc->numleafs;
 }
 
-template <int VW_THREADS>
-__device__ __forceinline__ void rc_stage_copy( void *dst, const void *src, size_t bytes, int t )
-{
-	uint4 *d = reinterpret_cast<uint4 *>( dst );
-	const uint4 *s = reinterpret_cast<const uint4 *>( src );
-	const size_t n = bytes / 16;
-	if( !n ) return;
-	/* every block copies the same bytes at the same time: start each one at a different place so that the
-	 * requests spread over the L2 slices instead of queueing on one */
-	const size_t rot = ((size_t)blockIdx.x * 37 ) % n;
-	size_t i = t;
-	for( ; i + 3 * VW_THREADS < n; i += 4 * VW_THREADS )
-	{
-		size_t i0 = i + rot, i1 = i0 + VW_THREADS, i2 = i1 + VW_THREADS, i3 = i2 + VW_THREADS;
-		if( i0 >= n ) i0 -= n; if( i1 >= n ) i1 -= n; if( i2 >= n ) i2 -= n; if( i3 >= n ) i3 -= n;
-		const uint4 a = s[i0], b = s[i1], c = s[i2], e = s[i3]; /* four loads in flight per thread */
-		d[i0] = a; d[i1] = b; d[i2] = c; d[i3] = e;
-	}
-	for( ; i < n; i += VW_THREADS )
-	{
-		size_t i0 = i + rot;
-		if( i0 >= n ) i0 -= n;
-		d[i0] = s[i0];
-	}
-}
+static_assert( sizeof( rc_node_t ) % 16 == 0 && sizeof( rc_plane_t ) % 16 == 0 && sizeof( rc_leaf_t ) % 16 == 0,
+	"the tree's tables are staged with 16-byte bulk copies" );
 
 /* frustum tests of one bbox against all four planes, no early out: bits 0..3 = trivially accepted, 4..7 = rejected */
 __device__ __forceinline__ int32_t rc_box_flags( const rc_view_t *vw, const float *minmaxs )
@@ -127,6 +104,7 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 	__shared__ int32_t s_pvsleaf[VW_PVSCAP];
 	__shared__ int32_t s_warp[VW_THREADS / 32];
 	__shared__ rc_view_t s_view;
+	__shared__ __align__( 8 ) unsigned long long s_bar; /* mbarrier of the tree's bulk copies */
 
 	const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
 #ifdef RC_SPANS_DEBUG
@@ -149,14 +127,25 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 	const uint16_t *sn16 = nullptr, *mk16 = nullptr;
 	{
 		unsigned char *p = reinterpret_cast<unsigned char *>( s_bits ) + (((size_t)allwords * 4 + 15 ) & ~(size_t)15 );
-		if( w.vis_stage & VW_STAGE_TREE )
+		const bool tree = ( w.vis_stage & VW_STAGE_TREE ) != 0;
+		if( tree )
 		{
-			rc_stage_copy<VW_THREADS>( p, sc.nodes, sizeof( rc_node_t ) * (size_t)sc.numnodes, t );
-			sc.nodes = reinterpret_cast<const rc_node_t *>( p ); p += sizeof( rc_node_t ) * (size_t)sc.numnodes;
-			rc_stage_copy<VW_THREADS>( p, sc.planes, sizeof( rc_plane_t ) * (size_t)sc.numplanes, t );
-			sc.planes = reinterpret_cast<const rc_plane_t *>( p ); p += sizeof( rc_plane_t ) * (size_t)sc.numplanes;
-			rc_stage_copy<VW_THREADS>( p, sc.leafs, sizeof( rc_leaf_t ) * (size_t)sc.numleafs, t );
-			sc.leafs = reinterpret_cast<const rc_leaf_t *>( p ); p += sizeof( rc_leaf_t ) * (size_t)sc.numleafs;
+			/* nodes, planes, leafs: bulk asynchronous copies issued by one thread (rc_bulk.cuh); the block goes on
+			 * with the 16-bit lists below while the bytes arrive, and waits on the mbarrier before the first view */
+			const uint32_t nb = (uint32_t)( sizeof( rc_node_t ) * (size_t)sc.numnodes ), pb = (uint32_t)( sizeof( rc_plane_t ) * (size_t)sc.numplanes ),
+				lb = (uint32_t)( sizeof( rc_leaf_t ) * (size_t)sc.numleafs );
+			if( t == 0 )
+			{
+				rc_mbar_init( &s_bar, 1 );
+				rc_mbar_expect_tx( &s_bar, nb + pb + lb );
+				rc_bulk_table_g2s( p, sc.nodes, nb, &s_bar, blockIdx.x );
+				rc_bulk_table_g2s( p + nb, sc.planes, pb, &s_bar, blockIdx.x );
+				rc_bulk_table_g2s( p + nb + pb, sc.leafs, lb, &s_bar, blockIdx.x );
+			}
+			sc.nodes = reinterpret_cast<const rc_node_t *>( p );
+			sc.planes = reinterpret_cast<const rc_plane_t *>( p + nb );
+			sc.leafs = reinterpret_cast<const rc_leaf_t *>( p + nb + pb );
+			p += nb + pb + lb;
 		}
 		if( w.vis_stage & VW_STAGE_SCRATCH )
 		{
@@ -169,6 +158,11 @@ __global__ void __launch_bounds__( VW_THREADS ) k_viswalk( rc_scene_t sc, rc_wor
 			for( int i = t; i < sc.numsurfaces; i += VW_THREADS ) a[i] = (uint16_t)sc.surfnode[i];
 			for( int i = t; i < sc.nummarks; i += VW_THREADS ) b[i] = (uint16_t)sc.marksurfaces[i];
 			sn16 = a; mk16 = b;
+		}
+		if( tree )
+		{
+			__syncthreads(); /* the barrier's initialisation is visible to every waiter */
+			rc_mbar_wait( &s_bar, 0 );
 		}
 	}
 	int32_t *e_ref = scr, *e_info = scr + cap, *e_child = scr + 2 * (size_t)cap, *e_size = scr + 3 * (size_t)cap;
