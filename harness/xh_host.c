@@ -269,6 +269,17 @@ static void xh_CL_DrawEFX( float time, qboolean trans )
 }
 
 /* fp: n x {x, y, z, colour index, die time, type} */
+void xh_decal_shoot( int texture, const float *pos, int flags, float scale )
+{
+	vec3_t p = { pos[0], pos[1], pos[2] };
+	xh.ref.R_DecalShoot( texture, 0, 0, p, flags, scale );
+}
+
+void xh_clear_decals( void )
+{
+	xh.ref.R_ClearAllDecals();
+}
+
 int xh_set_particles( const float *fp, int n )
 {
 	if( n > 4096 ) n = 4096;

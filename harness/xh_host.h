@@ -78,6 +78,9 @@ XH_EXPORT int xh_frame_views_hud( const float *cams, int n, float fov_x, float f
 	const float *hud, int nhud, void *display_out );
 XH_EXPORT int xh_screenshot( int shot_type, void *out, size_t cap, int *width, int *height );
 XH_EXPORT int xh_set_particles( const float *fp, int n );
+/* the renderer's R_DecalShoot slot on the world model (entity 0, model 0): decal texture, centre, FDECAL_* flags, scale */
+XH_EXPORT void xh_decal_shoot( int texture, const float *pos, int flags, float scale );
+XH_EXPORT void xh_clear_decals( void );
 XH_EXPORT void xh_light_point( const float *p, int *out );
 XH_EXPORT void xh_gamma_changed( float gamma, float brightness, float texgamma, float lightgamma );
 XH_EXPORT uint64_t xh_callback_count( void );            /* engine callbacks hit since init (debug) */

@@ -685,3 +685,17 @@ def test_particles_match_oracle(pkg, scene):
     rc, rz = so.render_views(m.cameras[:32])
     assert (rc != bare).mean() > 0.003
     assert np.array_equal(cc, rc) and np.array_equal(cz, rz), ((cc == rc).mean(), (cz == rz).mean())
+
+
+@pytest.mark.gpu
+def test_decal_shoot_matches_oracle(pkg, scene):
+    """R_DecalShoot through both plugins (ref_soft attaches no decal: tests/test_oracle.py::test_decal_shoot_leaves_frames_alone)"""
+    m = scene.make_map("tiny", ncameras=8)
+    cu = scene.Renderer(pkg.REF_CUDA_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    _, bz = so.render_views(m.cameras[:8])
+    for r in (cu, so):
+        scene.shoot_decals(r, m.cameras[:8], bz)
+    cc, cz = cu.render_views(m.cameras[:8])
+    rc, rz = so.render_views(m.cameras[:8])
+    assert np.array_equal(cc, rc) and np.array_equal(cz, rz)

@@ -245,3 +245,27 @@ def test_scalar_particles_match_oracle(pkg, scene):
     rc, rz = so.render_views(m.cameras[:12])
     assert (rc != bare).mean() > 0.003, "the oracle drew no particles"
     assert np.array_equal(a, rc) and np.array_equal(az, rz)
+
+
+def test_decal_shoot_leaves_frames_alone(pkg, scene):
+    """R_DecalShoot (ref/soft/r_decals.c:719) by executing the reference: ref_soft unlinks every decal again
+    (R_DecalVertsClip returns before writing the vertex count when surf->polys is NULL, which it always is in ref_soft;
+    r_decals.c:367, :578-583), so a shot changes no pixel and attaches nothing - and neither does ref/cuda's slot"""
+    import ctypes as C
+    m = scene.make_map("tiny", ncameras=8)
+    emu = scene.Renderer(EMU_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    before, bz = so.render_views(m.cameras[:8])
+    for r in (emu, so):
+        pts = scene.shoot_decals(r, m.cameras[:8], bz)
+    assert len(pts) == 8
+    after, az = so.render_views(m.cameras[:8])
+    assert np.array_equal(before, after) and np.array_equal(bz, az)
+    # the reference's decal pool: entries were taken (position written) and every one is detached (psurface NULL)
+    lib = C.CDLL(pkg.REF_SOFT_PATH)
+    pool = np.frombuffer((C.c_ubyte * (88 * 64)).in_dll(lib, "gDecalPool"), dtype=np.uint8).reshape(64, 88)
+    used = [e for e in pool if e.any()]
+    assert len(used) >= 8
+    assert all(not e[:16].any() for e in used), "a decal stayed linked to a surface: R_DrawSurfaceDecals has work, build N2"
+    a, z = emu.render_views(m.cameras[:8])
+    assert np.array_equal(a, after) and np.array_equal(z, az)

@@ -2433,6 +2433,15 @@ static colorVec R_LightPoint( const float *p )
 	colorVec c = { light[0], light[1], light[2], 255 };
 	return c;
 }
+/*
+ * R_DecalShoot (ref/soft/r_decals.c:719): ref_soft never attaches a decal to a surface.  R_DecalCreate (:554) keeps the
+ * pool entry only when R_DecalVertsClip (:356) reports clipped vertices, and that function returns at "if( !surf->polys )"
+ * (:367) before it writes the count - msurface_t::polys is built by ref_gl only, in ref_soft it is always NULL - so
+ * R_DecalCreate tests an uninitialised local (:578-583).  In the oracle build it reads 0: every decal is unlinked again,
+ * surf->pdecals stays empty and R_DrawSurfaceDecals (r_surf.c:914) has nothing to draw; frames before and after a shot
+ * are identical (tests/test_oracle.py::test_decal_shoot_leaves_frames_alone pins this by executing the reference).
+ * The observable behaviour - a shot changes no pixel and the decal list stays empty - is what this slot reproduces.
+ */
 static void R_DecalShoot( int textureIndex, int entityIndex, int modelIndex, vec3_t pos, int flags, float scale )
 { (void)textureIndex; (void)entityIndex; (void)modelIndex; (void)pos; (void)flags; (void)scale; }
 static void R_DecalRemoveAll( int texture ) { (void)texture; }

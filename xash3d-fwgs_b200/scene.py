@@ -89,6 +89,19 @@ class Renderer:
         L.xh_set_particles.argtypes = [C.c_void_p, C.c_int]
         return L.xh_set_particles(a.ctypes.data, len(a))
 
+    def decal_shoot(self, texture, pos, flags=0, scale=1.0):
+        """the renderer's R_DecalShoot slot on the world model: a decal texture (load_pic) stamped at pos"""
+        L = self.host.lib
+        L.xh_decal_shoot.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_float]
+        L.xh_decal_shoot.restype = None
+        pp = (C.c_float * 3)(*[float(x) for x in pos])
+        L.xh_decal_shoot(int(texture), pp, int(flags), float(scale))
+
+    def clear_decals(self):
+        L = self.host.lib
+        L.xh_clear_decals.restype = None
+        L.xh_clear_decals()
+
     def light_point(self, p):
         """the renderer's R_LightPoint slot: light of the world on the ground below p -> (r, g, b)"""
         L = self.host.lib
@@ -424,3 +437,26 @@ def compare_frames(a_col, a_z, b_col, b_z):
     same_c = float((a_col == b_col).mean())
     same_z = float((a_z == b_z).mean()) if a_z is not None and b_z is not None else 1.0
     return same_c, same_z
+
+
+def shoot_decals(r, cams, z, seed=5):
+    """R_DecalShoot at the point the middle pixel of every view in cams looks at (z: that renderer's 1/z frames of cams):
+    a 32x32 decal picture with an alpha channel, on the world model.  Returns the points."""
+    rng = np.random.default_rng(seed)
+    img = np.zeros((32, 32, 4), np.uint8)
+    img[..., 0] = 255
+    img[..., 1] = rng.integers(0, 255, (32, 32))
+    img[..., 3] = rng.integers(0, 255, (32, 32))
+    img[8:24, 8:24, 3] = 255
+    tex = r.load_pic("{decal1", img, 0)
+    pts = []
+    cams = np.asarray(cams, dtype=np.float32).reshape(-1, 6)
+    h, w = z.shape[1:3]
+    for i, c in enumerate(cams):
+        depth = 32768.0 / max(int(z[i, h // 2, w // 2]), 1)  # the z buffer holds 0x8000 / depth
+        p, y = np.radians(c[3]), np.radians(c[4])
+        fwd = np.array([np.cos(p) * np.cos(y), np.cos(p) * np.sin(y), -np.sin(p)])
+        pt = c[:3] + fwd * depth
+        r.decal_shoot(tex, pt, 0, 1.0)
+        pts.append(pt)
+    return pts
