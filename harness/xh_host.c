@@ -261,11 +261,68 @@ static void xh_R_StoreEfrags( struct efrag_s **pp, int framecount ) { (void)pp; 
 static particle_t xh_particles[4096];
 static int xh_nparticles;
 static void xh_CL_ThinkParticle( double frametime, particle_t *p ) { (void)frametime; (void)p; }
+/* tracers: the list the test set and the copy handed to the renderer, which moves them (CL_DrawTracers).  Every view is a
+ * frame of the same client state here, so each call starts from the list as set; xh_get_tracers reads the moved copy. */
+static particle_t xh_tracers_set[1024], xh_tracers[1024];
+static int xh_ntracers;
+static model_t *xh_dot_sprite;
+static model_t *xh_GetDefaultSprite( enum ref_defaultsprite_e spr ) { return spr == REF_DOT_SPRITE ? xh_dot_sprite : NULL; }
 static void xh_CL_DrawEFX( float time, qboolean trans )
 {
 	xh.callbacks++;
 	if( trans && xh_nparticles && xh.ref.CL_DrawParticles )
 		xh.ref.CL_DrawParticles( time, xh_particles, 2.0f ); /* PART_SIZE = max( 0.5, cl_draw_particles ): 2 keeps them visible at 320x240 */
+	if( trans && xh_ntracers && xh.ref.CL_DrawTracers )
+	{
+		memcpy( xh_tracers, xh_tracers_set, sizeof( particle_t ) * xh_ntracers );
+		for( int i = 0; i < xh_ntracers; i++ )
+			xh_tracers[i].next = i + 1 < xh_ntracers ? &xh_tracers[i + 1] : NULL;
+		xh.ref.CL_DrawTracers( time, xh_tracers );
+	}
+}
+
+/* the renderer's WorldToScreen slot (the view rendered last): out = {x, y, z}, returns its "behind the eye" flag */
+int xh_world_to_screen( const float *p, float *out )
+{
+	vec3_t w = { p[0], p[1], p[2] }, s = { 0, 0, 0 };
+	const int behind = xh.ref.WorldToScreen( w, s );
+	out[0] = s[0]; out[1] = s[1]; out[2] = s[2];
+	return behind;
+}
+
+/* the model GetDefaultSprite( REF_DOT_SPRITE ) answers with (the engine's sprites/dot.spr) */
+void xh_set_dot_sprite( int modelindex )
+{
+	xh_dot_sprite = ( modelindex > 0 && modelindex <= xh.cl.nummodels ) ? xh.cl.models[modelindex] : NULL;
+}
+
+/* fp: n x {org[3], vel[3], ramp, die, colour index, type, alpha (particle_t::unused)} */
+int xh_set_tracers( const float *fp, int n )
+{
+	if( n > 1024 ) n = 1024;
+	memset( xh_tracers_set, 0, sizeof( xh_tracers_set ));
+	for( int i = 0; i < n; i++ )
+	{
+		particle_t *p = &xh_tracers_set[i];
+		const float *f = fp + 11 * i;
+		p->org[0] = f[0]; p->org[1] = f[1]; p->org[2] = f[2];
+		p->vel[0] = f[3]; p->vel[1] = f[4]; p->vel[2] = f[5];
+		p->ramp = f[6]; p->die = f[7]; p->color = (short)f[8]; p->type = (ptype_t)(int)f[9]; p->unused = (short)f[10];
+	}
+	xh_ntracers = n;
+	return n;
+}
+
+/* the list as the renderer's last CL_DrawTracers call left it: n x {org[3], vel[3], alpha} */
+int xh_get_tracers( float *out )
+{
+	for( int i = 0; i < xh_ntracers; i++ )
+	{
+		const particle_t *p = &xh_tracers[i];
+		float *f = out + 7 * i;
+		f[0] = p->org[0]; f[1] = p->org[1]; f[2] = p->org[2]; f[3] = p->vel[0]; f[4] = p->vel[1]; f[5] = p->vel[2]; f[6] = (float)p->unused;
+	}
+	return xh_ntracers;
 }
 
 /* fp: n x {x, y, z, colour index, die time, type} */
@@ -464,7 +521,7 @@ static void xh_fill_engfuncs( ref_api_t *e )
 	e->pfnStudioEvent = (void *)xh_null_ptr;
 	e->pfnPlayerInfo = (void *)xh_null_ptr;
 	e->pfnGetPlayerState = (void *)xh_null_ptr;
-	e->GetDefaultSprite = (void *)xh_null_ptr;
+	e->GetDefaultSprite = (void *)xh_GetDefaultSprite;
 	e->R_GetSpriteFrame = (void *)xh_R_GetSpriteFrame;
 	e->R_StudioGetAnim = (void *)xh_R_StudioGetAnim;
 	e->CL_AllocElight = (void *)xh_null_ptr;

@@ -81,6 +81,11 @@ XH_EXPORT int xh_set_particles( const float *fp, int n );
 /* the renderer's R_DecalShoot slot on the world model (entity 0, model 0): decal texture, centre, FDECAL_* flags, scale */
 XH_EXPORT void xh_decal_shoot( int texture, const float *pos, int flags, float scale );
 XH_EXPORT void xh_clear_decals( void );
+/* tracers (CL_DrawTracers): the sprite model of REF_DOT_SPRITE, the client's active tracers, the list after the renderer moved it */
+XH_EXPORT int xh_world_to_screen( const float *p, float *out );
+XH_EXPORT void xh_set_dot_sprite( int modelindex );
+XH_EXPORT int xh_set_tracers( const float *fp, int n );
+XH_EXPORT int xh_get_tracers( float *out );
 XH_EXPORT void xh_light_point( const float *p, int *out );
 XH_EXPORT void xh_gamma_changed( float gamma, float brightness, float texgamma, float lightgamma );
 XH_EXPORT uint64_t xh_callback_count( void );            /* engine callbacks hit since init (debug) */

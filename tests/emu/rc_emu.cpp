@@ -374,10 +374,10 @@ static void emu_draw_items( const rc_view_t *vw, const emu_viewctx_t &cx, uint16
 		if( it->tex_ofs < 0 ) continue;
 		if( it->kind == RC_ITEM_BRUSH ) { emu_draw_tbrush( vw, cx, it->first, color, zb, width ); continue; }
 		rc_fv_t poly[8];
-		if( it->kind == RC_ITEM_SPRITE || it->kind == RC_ITEM_PARTICLE )
+		if( rc_item_is_quad( it ))
 		{
 			rc_corner_t q[4];
-			if( !( it->kind == RC_ITEM_SPRITE ? rc_sprite_corners( vw, it, q ) : rc_particle_corners( vw, it, q ))) continue;
+			if( !rc_quad_corners( vw, it, q )) continue;
 			int k = rc_view_triangle( vw, &q[0], &q[1], &q[2], poly );
 			if( k ) emu_draw_poly( it, poly, k, color, zb, width );
 			k = rc_view_triangle( vw, &q[0], &q[2], &q[3], poly );

@@ -699,3 +699,31 @@ def test_decal_shoot_matches_oracle(pkg, scene):
     cc, cz = cu.render_views(m.cameras[:8])
     rc, rz = so.render_views(m.cameras[:8])
     assert np.array_equal(cc, rc) and np.array_equal(cz, rz)
+
+
+@pytest.mark.gpu
+def test_tracers_match_oracle(pkg, scene):
+    """CL_DrawTracers on the device: 192 tracers (RC_ITEM_TRACER, quads per view from both ends' screen positions) with
+    particles and sprites in 32 views, some rolled, at two fields of view"""
+    m = scene.make_map("small", ncameras=64)
+    cu = scene.Renderer(pkg.REF_CUDA_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    cams = np.asarray(m.cameras[:32], dtype=np.float32).reshape(-1, 6).copy()
+    cams[::3, 5] = 20.0
+    bare, _ = so.render_views(cams)
+    for r in (cu, so):
+        r.set_time(1.0)
+        scene.add_tracers(r, cams, 192)
+        scene.add_particles(r, cams, 128, ahead=40.0)
+        add_test_sprites(r, m, m.cameras[:8], (2,))
+    for fov in (90.0, 70.0):
+        cc, cz = cu.render_views(cams, fov_x=fov)
+        rc, rz = so.render_views(cams, fov_x=fov)
+        assert np.array_equal(cc, rc) and np.array_equal(cz, rz), ((cc == rc).mean(), (cz == rz).mean(), fov)
+    assert (rc != bare).mean() > 0.003
+    n = 40
+    for r in (cu, so):
+        scene.add_tracers(r, cams[:4], n, moving=True, seed=3)
+    a = [r.render_views(cams[:1]) for r in (cu, so)]
+    assert np.array_equal(a[0][0], a[1][0])
+    assert np.array_equal(cu.get_tracers(n), so.get_tracers(n))

@@ -269,3 +269,57 @@ def test_decal_shoot_leaves_frames_alone(pkg, scene):
     assert all(not e[:16].any() for e in used), "a decal stayed linked to a surface: R_DrawSurfaceDecals has work, build N2"
     a, z = emu.render_views(m.cameras[:8])
     assert np.array_equal(a, after) and np.array_equal(z, az)
+
+
+def test_scalar_tracers_match_oracle(pkg, scene):
+    """CL_DrawTracers (ref/soft/r_part.c:137): streaks whose quads are widened at right angles to their direction
+    on the screen of every view (R_WorldToScreen through RI.worldviewProjectionMatrix, rc_view_wvp / rc_tracer_corners),
+    every colour and width of the function's tables - through the CPU debug harness, with roll and other fields of view"""
+    m = scene.make_map("small", ncameras=64)
+    emu = scene.Renderer(EMU_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    cams = np.asarray(m.cameras[:12], dtype=np.float32).reshape(-1, 6).copy()
+    cams[::3, 5] = 20.0  # roll
+    bare, _ = so.render_views(cams)
+    for r in (emu, so):
+        r.set_time(1.0)
+        scene.add_tracers(r, cams, 96)
+    for fov in (90.0, 70.0):
+        a, az = emu.render_views(cams, fov_x=fov)
+        rc, rz = so.render_views(cams, fov_x=fov)
+        assert np.array_equal(a, rc) and np.array_equal(az, rz), ((a == rc).mean(), fov)
+    assert (rc != bare).mean() > 0.002, "the oracle drew no tracers"
+
+
+def test_tracer_list_moves_as_the_reference_moves_it(pkg, scene):
+    """what CL_DrawTracers does to the client's list after drawing (r_part.c:236-253): positions advance by frametime,
+    pt_grav tracers lose speed and fade, pt_slowgrav ones get their fall speed - one view, so both plugins run it once"""
+    m = scene.make_map("tiny", ncameras=8)
+    emu = scene.Renderer(EMU_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    out = []
+    for r in (emu, so):
+        r.set_time(1.0)
+        n = scene.add_tracers(r, m.cameras[:4], 40, moving=True)
+        frame = r.render_views(m.cameras[:1])
+        out.append((r.get_tracers(n), frame))
+    assert np.array_equal(out[0][0], out[1][0])
+    assert np.array_equal(out[0][1][0], out[1][1][0])
+    assert len(np.unique(out[1][0][:, 6])) > 4
+
+
+def test_world_to_screen_slot_matches_oracle(pkg, scene):
+    """the WorldToScreen slot (R_WorldToScreen, ref/soft/r_main.c:210) after a view: every camera position of the map seen from
+    three views (fields of view 90 and 60, one rolled) answers as ref_soft does, bit for bit, behind-the-eye flag included"""
+    m = scene.make_map("small", ncameras=64)
+    emu = scene.Renderer(EMU_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    cams = np.asarray(m.cameras[:3], dtype=np.float32).reshape(-1, 6).copy()
+    cams[2, 5] = 33.0
+    for i, fov in enumerate((90.0, 60.0, 90.0)):
+        got, want = [], []
+        for r, acc in ((emu, got), (so, want)):
+            r.render_views(cams[i:i + 1], fov_x=fov)
+            acc.extend(r.world_to_screen(c[:3]) for c in m.cameras[:64])
+        assert got == want
+        assert 0 < sum(w[0] for w in want) < 64

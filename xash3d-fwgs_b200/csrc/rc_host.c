@@ -100,6 +100,7 @@ static struct
 	/* view queue between R_BeginFrame and R_EndFrame */
 	rc_view_t   *views;
 	int          nviews, maxviews;
+	float        last_wvp[3][4];  /* rows 0, 1, 3 of RI.worldviewProjectionMatrix of the view set up last (WorldToScreen slot) */
 	int          particleTexture; /* tr.particleTexture: the engine's "*particle" builtin, remembered by name (r_image.c:646) */
 	int          screen_view, screen_valid; /* the frame of the last batch R_EndFrame showed (VID_ScreenShot) */
 	rc_cmd2d_t  *cmds2d; int ncmds2d, maxcmds2d; /* the frame's HUD pass (R_DrawStretchPic / FillRGBA), applied in R_EndFrame */
@@ -664,6 +665,74 @@ static void CL_RunLightStyles( lightstyle_t *ls )
 /* per-view constants                                                                               */
 
 /*
+ * RI.worldviewProjectionMatrix (ref/soft/r_main.c:405-435, 1078-1081; ref/common/ref_math.c): the GL-style projection
+ * times the quake-to-GL axis swap, rotated by -roll, -pitch, -yaw and moved by -vieworigin.  Only R_WorldToScreen reads
+ * it (tracers, the WorldToScreen slot).  4x4 products with the reference's summation order, rotations by its formula.
+ */
+typedef float rc_m44_t[4][4];
+
+static void rc_m44_mul( rc_m44_t out, rc_m44_t a, rc_m44_t b )
+{
+	rc_m44_t r;
+	for( int i = 0; i < 4; i++ )
+		for( int j = 0; j < 4; j++ )
+			r[i][j] = a[i][0] * b[0][j] + a[i][1] * b[1][j] + a[i][2] * b[2][j] + a[i][3] * b[3][j];
+	memcpy( out, r, sizeof( r ));
+}
+
+/* m = m * rotation by `angle` degrees about the axis (x, y, z) (Matrix4x4_ConcatRotate) */
+static void rc_m44_rotate( rc_m44_t m, float angle, float x, float y, float z )
+{
+	float len = x * x + y * y + z * z;
+	if( len != 0.0f )
+		len = 1.0f / sqrt( len );
+	x *= len; y *= len; z *= len;
+	float c, s;
+	angle *= ( -M_PI_F / 180.0f );
+	SinCos( angle, &s, &c );
+	rc_m44_t r = {
+		{ x * x + c * ( 1 - x * x ), x * y * ( 1 - c ) + z * s, z * x * ( 1 - c ) - y * s, 0.0f },
+		{ x * y * ( 1 - c ) - z * s, y * y + c * ( 1 - y * y ), y * z * ( 1 - c ) + x * s, 0.0f },
+		{ z * x * ( 1 - c ) + y * s, y * z * ( 1 - c ) - x * s, z * z + c * ( 1 - z * z ), 0.0f },
+		{ 0.0f, 0.0f, 0.0f, 1.0f } };
+	rc_m44_mul( m, m, r );
+}
+
+static void rc_view_wvp( const ref_viewpass_t *rvp, rc_view_t *v )
+{
+	/* R_SetupModelviewMatrix: x right / y up / -z forward out of quake's x forward / y left / z up */
+	rc_m44_t mv = { { 0.0f, -1.0f, 0.0f, 0.0f }, { 0.0f, 0.0f, 1.0f, 0.0f }, { -1.0f, 0.0f, 0.0f, 0.0f }, { 0.0f, 0.0f, 0.0f, 1.0f } };
+	rc_m44_rotate( mv, -rvp->viewangles[2], 1, 0, 0 );
+	rc_m44_rotate( mv, -rvp->viewangles[0], 0, 1, 0 );
+	rc_m44_rotate( mv, -rvp->viewangles[1], 0, 0, 1 );
+	rc_m44_t tr = { { 1.0f, 0.0f, 0.0f, -rvp->vieworigin[0] }, { 0.0f, 1.0f, 0.0f, -rvp->vieworigin[1] },
+		{ 0.0f, 0.0f, 1.0f, -rvp->vieworigin[2] }, { 0.0f, 0.0f, 0.0f, 1.0f } };
+	rc_m44_mul( mv, mv, tr );
+
+	/* R_SetupProjectionMatrix, R_GetFarClip */
+	const movevars_t *mvars = (const movevars_t *)gEngfuncs.EngineGetParm( PARM_GET_MOVEVARS_PTR, 0 );
+	const float farclip = ( rc.world && FBitSet( rvp->flags, RF_DRAW_WORLD ) && mvars ) ? mvars->zmax * 1.73f : 2048.0f;
+	const float zNear = 4.0f, zFar = Q_max( 256.0f, farclip );
+	const float yMax = zNear * tan( rvp->fov_y * M_PI_F / 360.0f ), yMin = -yMax;
+	const float xMax = zNear * tan( rvp->fov_x * M_PI_F / 360.0f ), xMin = -xMax;
+	rc_m44_t pr;
+	memset( pr, 0, sizeof( pr ));
+	pr[0][0] = ( 2.0f * zNear ) / ( xMax - xMin );
+	pr[1][1] = ( 2.0f * zNear ) / ( yMax - yMin );
+	pr[2][2] = -( zFar + zNear ) / ( zFar - zNear );
+	pr[0][2] = ( xMax + xMin ) / ( xMax - xMin );
+	pr[1][2] = ( yMax + yMin ) / ( yMax - yMin );
+	pr[3][2] = -1.0f;
+	pr[2][3] = -( 2.0f * zFar * zNear ) / ( zFar - zNear );
+
+	rc_m44_t wvp;
+	rc_m44_mul( wvp, pr, mv );
+	memcpy( v->wvp[0], wvp[0], sizeof( wvp[0] ));
+	memcpy( v->wvp[1], wvp[1], sizeof( wvp[1] ));
+	memcpy( v->wvp[2], wvp[3], sizeof( wvp[3] ));
+}
+
+/*
  * R_SetupFrustum (ref/soft/r_main.c:387) + R_SetupFrameQ / R_ViewChanged / R_TransformFrustum /
  * R_SetUpFrustumIndexes (r_misc.c:101-322) for one ref_viewpass_t, with the reference's float
  * expression order and this host's libm (tgmath: tan on a float argument is tanf).
@@ -770,6 +839,8 @@ static void rc_setup_view( const ref_viewpass_t *rvp, rc_view_t *v )
 	v->texfilt = sw_texfilt.value == 1.0f;
 	v->flags = rvp->flags;
 	v->pvs_radius = r_novis.value ? -1.0f : r_pvs_radius->value;
+	rc_view_wvp( rvp, v );
+	memcpy( rc.last_wvp, v->wvp, sizeof( rc.last_wvp ));
 }
 
 /* ---------------------------------------------------------------------------------------------- */
@@ -2360,7 +2431,23 @@ static void rc_flush_2d( int view )
 	rc.ncmds2d = 0;
 }
 
-static int WorldToScreen( const vec3_t world, vec3_t screen ) { (void)world; VectorClear( screen ); return 1; }
+/* R_WorldToScreen (ref/soft/r_main.c:210) against the matrix of the view set up last, as RI keeps it between frames */
+static int WorldToScreen( const vec3_t world, vec3_t screen )
+{
+	if( !world || !screen )
+		return true;
+	const float ( *m )[4] = rc.last_wvp;
+	screen[0] = m[0][0] * world[0] + m[0][1] * world[1] + m[0][2] * world[2] + m[0][3];
+	screen[1] = m[1][0] * world[0] + m[1][1] * world[1] + m[1][2] * world[2] + m[1][3];
+	const float w = m[2][0] * world[0] + m[2][1] * world[1] + m[2][2] * world[2] + m[2][3];
+	screen[2] = 0.0f;
+	if( w < 0.001f )
+		return true;
+	const float invw = 1.0f / w;
+	screen[0] *= invw;
+	screen[1] *= invw;
+	return false;
+}
 /* VID_ScreenShot (ref/soft/r_glblit.c:748): the frame last shown, in display colours, bottom row first, as PF_BGRA_32
  * through the engine's image writer.  The frame is still in HBM: k_blit converts it once more, into the shot. */
 static qboolean VID_ScreenShot( const char *filename, int shot_type )
@@ -2520,7 +2607,92 @@ static void CL_DrawParticles( double frametime, particle_t *particles, float par
 		gEngfuncs.CL_ThinkParticle( frametime, p );
 	}
 }
-static void CL_DrawTracers( double frametime, particle_t *tracers ) { (void)frametime; (void)tracers; }
+
+/*
+ * CL_DrawTracers (ref/soft/r_part.c:137): a tracer is a streak from p->org along p->vel; its quad is as wide as
+ * gTracerSize says, at right angles to the streak's direction ON THE SCREEN of the view that draws it (R_WorldToScreen of
+ * both ends).  The host records one item per tracer - start, streak vector, half width, colour - and every view builds
+ * its own quad on the device (rc_tracer_corners); ref_soft culls none (CL_CullTracer returns false).  The movement the
+ * function applies to the client's list afterwards stays here.
+ */
+static const float rc_tracer_size[11] = { 1.5f, 0.5f, 1.0f, 1.0f, 1.0f, 1.0f, 1.0f, 1.0f, 1.0f, 1.0f, 1.0f };
+static color24 rc_tracer_colors[12] =
+{
+	{ 255, 255, 255 }, { 255, 0, 0 }, { 0, 255, 0 }, { 0, 0, 255 },
+	{ 0, 0, 0 },       /* TRACER_COLORINDEX_DEFAULT: from tracerred / tracergreen / tracerblue / traceralpha */
+	{ 255, 167, 17 }, { 255, 130, 90 }, { 55, 60, 144 }, { 255, 130, 90 }, { 255, 140, 90 }, { 200, 130, 90 }, { 255, 120, 70 },
+};
+
+static void CL_DrawTracers( double frametime, particle_t *tracers )
+{
+	if( FBitSet( tracerred->flags | tracergreen->flags | tracerblue->flags | traceralpha->flags, FCVAR_CHANGED ))
+	{
+		color24 *custom = &rc_tracer_colors[4];
+		custom->r = (byte)( tracerred->value * traceralpha->value * 255 );
+		custom->g = (byte)( tracergreen->value * traceralpha->value * 255 );
+		custom->b = (byte)( tracerblue->value * traceralpha->value * 255 );
+		ClearBits( tracerred->flags, FCVAR_CHANGED );
+		ClearBits( tracergreen->flags, FCVAR_CHANGED );
+		ClearBits( tracerblue->flags, FCVAR_CHANGED );
+		ClearBits( traceralpha->flags, FCVAR_CHANGED );
+	}
+	if( !tracers )
+		return;
+	GL_SetRenderMode( kRenderTransAdd );
+	/* TriSpriteTexture( GetDefaultSprite( REF_DOT_SPRITE ), 0 ), r_triapi.c:282 */
+	model_t *dot = gEngfuncs.GetDefaultSprite( REF_DOT_SPRITE );
+	if( !dot || dot->type != mod_sprite || !dot->cache.data )
+		return;
+	int texnum = gEngfuncs.R_GetSpriteFrame( dot, 0, 0.0f )->gl_texturenum;
+	if( texnum == 0 )
+		return;
+	if( texnum < 0 || texnum >= RC_MAX_TEXTURES )
+		texnum = 0;
+	GL_Bind( XASH_TEXTURE0, texnum );
+
+	const movevars_t *mv = (const movevars_t *)gEngfuncs.EngineGetParm( PARM_GET_MOVEVARS_PTR, 0 );
+	const float gravity = frametime * ( mv ? mv->gravity : 800.0f );
+	float scale = 1.0 - ( frametime * 0.9 );
+	if( scale < 0.0f )
+		scale = 0.0f;
+	for( particle_t *p = tracers; p; p = p->next )
+	{
+		float atten = ( p->die - gp_cl->time );
+		if( atten > 0.1f )
+			atten = 0.1f;
+		vec3_t delta;
+		VectorScale( p->vel, ( p->ramp * atten ), delta );
+		const short alpha = p->unused;
+		if( p->color < 0 || p->color >= (int)( sizeof( rc_tracer_colors ) / sizeof( rc_tracer_colors[0] )))
+			p->color = TRACER_COLORINDEX_DEFAULT;
+		const color24 color = rc_tracer_colors[p->color];
+		rc_tri_color4f( 1.0f * alpha / 255 / 255 * color.r, 1.0f * alpha / 255 / 255 * color.g, 1.0f * alpha / 255 / 255 * color.b, 1.0f );
+		rc_item_t *it = rc_new_item( RC_ITEM_TRACER );
+		it->count = 2;
+		it->light = (int32_t)( rc.tri.light << 8 );
+		it->scale = rc_tracer_size[p->type];
+		VectorCopy( p->org, it->origin );
+		VectorCopy( delta, it->angles );
+		TriTexCoord2f( 0.0f, 0.0f ); it->s0 = rc.tri.s; it->t0 = rc.tri.t;
+		TriTexCoord2f( 1.0f, 0.8f ); it->s1 = rc.tri.s; it->t1 = rc.tri.t;
+
+		/* the client's list moves on */
+		VectorMA( p->org, frametime, p->vel, p->org );
+		if( p->type == pt_grav )
+		{
+			p->vel[0] *= scale;
+			p->vel[1] *= scale;
+			p->vel[2] -= gravity;
+			p->unused = 255 * ( p->die - gp_cl->time ) * 2;
+			if( p->unused > 255 )
+				p->unused = 255;
+		}
+		else if( p->type == pt_slowgrav )
+		{
+			p->vel[2] = gravity * 0.05;
+		}
+	}
+}
 static void CL_DrawBeams( int fTrans, BEAM *beams ) { (void)fTrans; (void)beams; }
 
 static intptr_t RefGetParm( int parm, int arg )

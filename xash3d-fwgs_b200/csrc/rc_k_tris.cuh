@@ -79,10 +79,10 @@ __global__ void __launch_bounds__( 128 ) k_item_order( rc_work_t w )
 /* world-space corners of triangle tri of an item for a view; 0 = not drawn */
 __device__ __forceinline__ int rc_item_corners( const rc_work_t &w, const rc_view_t *vw, const rc_item_t *it, int32_t tri, rc_corner_t *c )
 {
-	if( it->kind == RC_ITEM_SPRITE || it->kind == RC_ITEM_PARTICLE )
+	if( rc_item_is_quad( it ))
 	{
 		rc_corner_t q[4];
-		if( !( it->kind == RC_ITEM_SPRITE ? rc_sprite_corners( vw, it, q ) : rc_particle_corners( vw, it, q )))
+		if( !rc_quad_corners( vw, it, q ))
 			return 0;
 		c[0] = q[0];
 		c[1] = tri ? q[2] : q[1];

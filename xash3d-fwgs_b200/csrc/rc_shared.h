@@ -158,6 +158,7 @@ typedef struct
 	int32_t flags;               /* ref_viewpass_t.flags */
 	float   pvs_radius;
 	float   screenedge[4][3];    /* qfrustum.screenedge normals (view space): R_TransformFrustum runs again per brush entity */
+	float   wvp[3][4];           /* rows 0, 1 and 3 of RI.worldviewProjectionMatrix (r_main.c:1078-1081): R_WorldToScreen */
 	int32_t texfilt;             /* sw_texfilt == 1: D_DrawSpans16's texture dither (ref/soft/r_scan.c:503-672) */
 	float   aliastransform[3][4]; /* R_SetUpWorldTransform (ref/soft/r_trialias.c:52): world -> view space for R_SetupFinalVert */
 } rc_view_t;
@@ -168,7 +169,9 @@ typedef struct
  * draws in; translucent entities come with a sort record, their order is per view (R_TransEntityCompare, r_main.c:157).
  */
 enum { RC_ITEM_TRIS = 0, RC_ITEM_SPRITE = 1, RC_ITEM_MESH = 2, RC_ITEM_BRUSH = 3 /* a translucent brush entity: first = its rc_bent_t */,
-	RC_ITEM_PARTICLE = 4 /* a particle of CL_DrawParticles: a quad that faces every view (origin, scale = partsize) */ };
+	RC_ITEM_PARTICLE = 4 /* a particle of CL_DrawParticles: a quad that faces every view (origin, scale = partsize) */,
+	RC_ITEM_TRACER = 5 /* a tracer of CL_DrawTracers: a quad along the streak, as wide as its direction on the screen of every
+	                    * view says (origin = start, angles = the streak's vector, scale = gTracerSize of its type) */ };
 /* the span drawer a texture bind selects (GL_Bind, ref/soft/r_image.c:43-75): R_PolysetFillSpans8, ...Additive, ...Glow,
  * ...TextureBlended, ...Blended (r_polyse.c:724-1214) */
 enum { RC_DRAW_FILL = 0, RC_DRAW_ADDITIVE = 1, RC_DRAW_GLOW = 2, RC_DRAW_TEXBLEND = 3, RC_DRAW_BLEND = 4 };

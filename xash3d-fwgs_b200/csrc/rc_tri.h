@@ -753,6 +753,66 @@ RC_HD int rc_particle_corners( const rc_view_t *vw, const rc_item_t *it, rc_corn
 	return 1;
 }
 
+/* R_WorldToScreen (r_main.c:210): x, y of a world point in the view's clip space; not divided for points behind the eye */
+RC_HD void rc_world_to_screen( const rc_view_t *vw, const float *p, float *screen )
+{
+	screen[0] = vw->wvp[0][0] * p[0] + vw->wvp[0][1] * p[1] + vw->wvp[0][2] * p[2] + vw->wvp[0][3];
+	screen[1] = vw->wvp[1][0] * p[0] + vw->wvp[1][1] * p[1] + vw->wvp[1][2] * p[2] + vw->wvp[1][3];
+	const float w = vw->wvp[2][0] * p[0] + vw->wvp[2][1] * p[1] + vw->wvp[2][2] * p[2] + vw->wvp[2][3];
+	screen[2] = 0.0f;
+	if( !( w < 0.001f ))
+	{
+		const float invw = 1.0f / w;
+		screen[0] *= invw;
+		screen[1] *= invw;
+	}
+}
+
+/* a tracer's quad for a view (CL_DrawTracers, r_part.c:183-232): the streak start .. start + delta, widened at right
+ * angles to its direction on this view's screen.  Corners in the order the reference submits them (TRI_QUADS). */
+RC_HD int rc_tracer_corners( const rc_view_t *vw, const rc_item_t *it, rc_corner_t *q )
+{
+	const float *start = it->origin, *delta = it->angles;
+	float end[3], screen[3], screen_last[3], tmp[3], normal[3], tmp2[3], verts[4][3];
+	for( int k = 0; k < 3; k++ ) end[k] = start[k] + delta[k];
+	rc_world_to_screen( vw, start, screen );
+	rc_world_to_screen( vw, end, screen_last );
+	tmp[0] = screen[0] - screen_last[0]; tmp[1] = screen[1] - screen_last[1]; tmp[2] = 0.0f;
+	rc_vec_normalize( tmp );
+	const float su = tmp[0] * it->scale, sr = -tmp[1] * it->scale;
+	for( int k = 0; k < 3; k++ )
+	{
+		normal[k] = vw->vup[k] * su;
+		tmp2[k] = vw->vright[k] * sr;
+		normal[k] = normal[k] - tmp2[k];
+		verts[0][k] = start[k] - normal[k];
+		verts[1][k] = start[k] + normal[k];
+		verts[2][k] = verts[0][k] + delta[k];
+		verts[3][k] = verts[1][k] + delta[k];
+	}
+	/* TriTexCoord2f( 0, 0.8 ) verts[2], ( 1, 0.8 ) verts[3], ( 1, 0 ) verts[1], ( 0, 0 ) verts[0]; t1 = the texel of 0.8 */
+	for( int k = 0; k < 3; k++ ) { q[0].xyz[k] = verts[2][k]; q[1].xyz[k] = verts[3][k]; q[2].xyz[k] = verts[1][k]; q[3].xyz[k] = verts[0][k]; }
+	q[0].s = it->s0; q[0].t = it->t1; q[1].s = it->s1; q[1].t = it->t1; q[2].s = it->s1; q[2].t = it->t0; q[3].s = it->s0; q[3].t = it->t0;
+	for( int k = 0; k < 4; k++ ) q[k].l = it->light;
+	return 1;
+}
+
+/* the items that are one quad built per view */
+RC_HD int rc_item_is_quad( const rc_item_t *it )
+{
+	return it->kind == RC_ITEM_SPRITE || it->kind == RC_ITEM_PARTICLE || it->kind == RC_ITEM_TRACER;
+}
+
+RC_HD int rc_quad_corners( const rc_view_t *vw, const rc_item_t *it, rc_corner_t *q )
+{
+	switch( it->kind )
+	{
+	case RC_ITEM_SPRITE: return rc_sprite_corners( vw, it, q );
+	case RC_ITEM_PARTICLE: return rc_particle_corners( vw, it, q );
+	default: return rc_tracer_corners( vw, it, q );
+	}
+}
+
 /*
  * One triangle of a draw item for one view, as the reference draws it: corners -> R_SetupFinalVert ->
  * R_RenderTriangle (trivial reject, R_AliasClipTriangle).  poly receives the vertices of the polygon to draw (3 when

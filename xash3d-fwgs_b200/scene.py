@@ -89,6 +89,34 @@ class Renderer:
         L.xh_set_particles.argtypes = [C.c_void_p, C.c_int]
         return L.xh_set_particles(a.ctypes.data, len(a))
 
+    def world_to_screen(self, p):
+        """the renderer's WorldToScreen slot for the view rendered last -> (behind, x, y)"""
+        L = self.host.lib
+        L.xh_world_to_screen.argtypes = [C.c_void_p, C.c_void_p]
+        pp = (C.c_float * 3)(*[float(x) for x in p])
+        out = (C.c_float * 3)()
+        b = L.xh_world_to_screen(pp, out)
+        return (int(b), float(out[0]), float(out[1]))
+
+    def set_tracers(self, rows, dot_model):
+        """the client's active tracers: rows of {org[3], vel[3], ramp, die, colour index, ptype_t, alpha}; drawn by
+        CL_DrawTracers in every following view with the sprite model dot_model as REF_DOT_SPRITE"""
+        a = np.ascontiguousarray(np.asarray(rows, dtype=np.float32).reshape(-1, 11))
+        L = self.host.lib
+        L.xh_set_dot_sprite.argtypes = [C.c_int]
+        L.xh_set_dot_sprite.restype = None
+        L.xh_set_dot_sprite(int(dot_model))
+        L.xh_set_tracers.argtypes = [C.c_void_p, C.c_int]
+        return L.xh_set_tracers(a.ctypes.data, len(a))
+
+    def get_tracers(self, n):
+        """the tracer list as the renderer's last CL_DrawTracers call left it: rows of {org[3], vel[3], alpha}"""
+        out = np.zeros((n, 7), np.float32)
+        L = self.host.lib
+        L.xh_get_tracers.argtypes = [C.c_void_p]
+        got = L.xh_get_tracers(out.ctypes.data)
+        return out[:got]
+
     def decal_shoot(self, texture, pos, flags=0, scale=1.0):
         """the renderer's R_DecalShoot slot on the world model: a decal texture (load_pic) stamped at pos"""
         L = self.host.lib
@@ -400,6 +428,34 @@ def add_particles(r, cams, count=256, ahead=60.0, seed=5):
         rows.append([c[0] + dist * math.cos(yaw) + off[0], c[1] + dist * math.sin(yaw) + off[1], c[2] + off[2] * 0.5,
                      int(rng.integers(40, 256)), 1.0 + [10.0, 0.03, 0.05][k % 3], [0, 0, 6][k % 3]])  # pt_static, pt_static fading, pt_fire
     return r.set_particles(rows)
+
+
+def add_tracers(r, cams, count=64, ahead=70.0, seed=9, moving=False):
+    """`count` tracers in front of the cameras: streaks in random directions, every colour and width of CL_DrawTracers' tables.
+    moving=False keeps to the particle types the function leaves alone (it is called once per view by ref_soft and once per
+    batch by ref/cuda); moving=True adds pt_grav / pt_slowgrav, whose velocity and alpha it rewrites."""
+    rng = np.random.default_rng(seed)
+    d = np.zeros((16, 16, 4), np.uint8)
+    yy, xx = np.mgrid[0:16, 0:16]
+    d[..., 0] = d[..., 1] = d[..., 2] = np.clip(255 - 28 * np.hypot(xx - 7.5, yy - 7.5), 0, 255).astype(np.uint8)
+    d[..., 1] = (d[..., 1] * (0.5 + 0.5 * rng.random((16, 16)))).astype(np.uint8)
+    d[..., 3] = 255
+    dot = r.create_sprite("spr_dot", d, sprtype=2, texformat=1)
+    cams = np.asarray(cams, dtype=np.float32).reshape(-1, 6)
+    types = [0, 3, 5, 6, 9] + ([1, 2] if moving else [])  # pt_static, pt_fire, pt_explode2, pt_blob, ... (+ pt_grav, pt_slowgrav)
+    rows = []
+    for k in range(count):
+        c = cams[k % len(cams)]
+        yaw = math.radians(float(c[4]))
+        off = rng.uniform(-30, 30, 3)
+        dist = ahead + 12.0 * (k // len(cams))
+        vel = rng.uniform(-1, 1, 3)
+        vel *= rng.uniform(200, 900) / np.linalg.norm(vel)
+        rows.append([c[0] + dist * math.cos(yaw) + off[0], c[1] + dist * math.sin(yaw) + off[1], c[2] + off[2] * 0.4,
+                     vel[0], vel[1], vel[2], rng.uniform(0.5, 1.5), 1.0 + [10.0, 0.04, 0.07][k % 3],
+                     int(rng.integers(-1, 13)), types[k % len(types)], int(rng.integers(60, 256))])
+    r.set_tracers(rows, dot)
+    return len(rows)
 
 
 def sprite_image(seed, w=64, h=64):
