@@ -290,6 +290,33 @@ int xh_world_to_screen( const float *p, float *out )
 	return behind;
 }
 
+/* EV_VisTraceLine for the glow sprites' sight line (engine/client/cl_game.c): this harness has no collision hulls - the
+ * line is stopped by one wall the test places, the plane coordinate[axis] = dist (axis < 0: nothing in the way) */
+static int xh_wall_axis = -1;
+static float xh_wall_dist;
+static pmtrace_t xh_vistrace;
+static pmtrace_t *xh_EV_VisTraceLine( float *start, float *end, int flags )
+{
+	(void)flags;
+	xh.callbacks++;
+	memset( &xh_vistrace, 0, sizeof( xh_vistrace ));
+	xh_vistrace.fraction = 1.0f;
+	if( xh_wall_axis >= 0 && xh_wall_axis < 3 )
+	{
+		const float a = start[xh_wall_axis] - xh_wall_dist, b = end[xh_wall_axis] - xh_wall_dist;
+		if(( a < 0 ) != ( b < 0 ) && a != b )
+			xh_vistrace.fraction = a / ( a - b );
+	}
+	for( int i = 0; i < 3; i++ )
+		xh_vistrace.endpos[i] = start[i] + xh_vistrace.fraction * ( end[i] - start[i] );
+	return &xh_vistrace;
+}
+
+void xh_set_sight_wall( int axis, float dist )
+{
+	xh_wall_axis = axis; xh_wall_dist = dist;
+}
+
 /* the model GetDefaultSprite( REF_DOT_SPRITE ) answers with (the engine's sprites/dot.spr) */
 void xh_set_dot_sprite( int modelindex )
 {
@@ -522,6 +549,7 @@ static void xh_fill_engfuncs( ref_api_t *e )
 	e->pfnPlayerInfo = (void *)xh_null_ptr;
 	e->pfnGetPlayerState = (void *)xh_null_ptr;
 	e->GetDefaultSprite = (void *)xh_GetDefaultSprite;
+	e->EV_VisTraceLine = xh_EV_VisTraceLine;
 	e->R_GetSpriteFrame = (void *)xh_R_GetSpriteFrame;
 	e->R_StudioGetAnim = (void *)xh_R_StudioGetAnim;
 	e->CL_AllocElight = (void *)xh_null_ptr;

@@ -83,6 +83,8 @@ XH_EXPORT void xh_decal_shoot( int texture, const float *pos, int flags, float s
 XH_EXPORT void xh_clear_decals( void );
 /* tracers (CL_DrawTracers): the sprite model of REF_DOT_SPRITE, the client's active tracers, the list after the renderer moved it */
 XH_EXPORT int xh_world_to_screen( const float *p, float *out );
+/* the wall EV_VisTraceLine finds (glow sprites): the plane coordinate[axis] = dist; axis < 0 removes it */
+XH_EXPORT void xh_set_sight_wall( int axis, float dist );
 XH_EXPORT void xh_set_dot_sprite( int modelindex );
 XH_EXPORT int xh_set_tracers( const float *fp, int n );
 XH_EXPORT int xh_get_tracers( float *out );

@@ -29,6 +29,7 @@ struct Emu
 	std::vector<int32_t> sintable, sedgepartner; std::vector<float> sedgeverts;
 	std::vector<uint16_t> alphamap; std::vector<uint8_t> addmap, modmap;
 	std::vector<rc_item_t> items; std::vector<rc_corner_t> corners; std::vector<rc_sortent_t> sortents;
+	std::vector<rc_glow_t> glow; int nglow = 0;
 	std::vector<rc_bent_t> bents;
 	std::vector<uint8_t> sstatic; std::vector<rc_spart_t> parts; std::vector<float> bones, blight, mvpos; std::vector<int32_t> mlight;
 	int32_t styles[256];
@@ -328,7 +329,7 @@ static void emu_draw_tbrush( const rc_view_t *vw, const emu_viewctx_t &cx, int32
 	if( ovf ) E.counters[RC_CTR_OVERFLOW_EVENTS]++;
 }
 
-static void emu_draw_items( const rc_view_t *vw, const emu_viewctx_t &cx, uint16_t *color, int16_t *zb, int width, int height )
+static void emu_draw_items( const rc_view_t *vw, int vi, const emu_viewctx_t &cx, uint16_t *color, int16_t *zb, int width, int height )
 {
 	if( E.items.empty() || !color || !zb )
 		return;
@@ -377,6 +378,15 @@ static void emu_draw_items( const rc_view_t *vw, const emu_viewctx_t &cx, uint16
 		if( rc_item_is_quad( it ))
 		{
 			rc_corner_t q[4];
+			rc_item_t gi;
+			if( it->glow >= 0 )
+			{
+				/* a glow sprite: this view's verdict, size and colour */
+				const rc_glow_t &g = E.glow[(size_t)vi * E.nglow + it->glow];
+				if( !g.visible ) continue;
+				gi = *it; gi.scale = g.scale; gi.light = g.light; gi.color = g.color; gi.alpha = g.alpha;
+				it = &gi;
+			}
 			if( !rc_quad_corners( vw, it, q )) continue;
 			int k = rc_view_triangle( vw, &q[0], &q[1], &q[2], poly );
 			if( k ) emu_draw_poly( it, poly, k, color, zb, width );
@@ -615,7 +625,7 @@ int rc_dev_render( const rc_view_t *views, int nviews, int width, int height, in
 		}
 		{
 			emu_viewctx_t cx = { nodevis.data(), leafmark.data(), leafbase.data(), leafkey.data(), candof.data() };
-			emu_draw_items( vw, cx, color, zb, width, height );
+			emu_draw_items( vw, vi, cx, color, zb, width, height );
 		}
 		E.vsurfs[vi] = surfs; E.vedges[vi] = edges;
 		E.counters[RC_CTR_VIEWS]++; E.counters[RC_CTR_PIXELS] += (uint64_t)vw_w * vw_h;
@@ -633,6 +643,12 @@ int rc_dev_set_dlights( const rc_dlight_t *, int n ) { return n ? -1 : 0; }
 
 /* the display tail is not part of the debug harness (it keeps no frames) */
 int rc_dev_set_screenmap( const uint32_t *, int ) { return 0; }
+int rc_dev_set_glow( const rc_glow_t *recs, int nglow, int nviews )
+{
+	E.nglow = nglow > 0 ? nglow : 0;
+	E.glow.assign( recs, recs + (size_t)E.nglow * ( nviews > 0 ? nviews : 0 ));
+	return 0;
+}
 int rc_dev_set_bents( const rc_bent_t *bents, int n ) { E.bents.assign( bents, bents + ( n > 0 ? n : 0 )); return 0; }
 int rc_dev_draw2d( const rc_cmd2d_t *, int, int ) { snprintf( E.err, sizeof( E.err ), "HUD pass: not in the debug harness" ); return -1; }
 int rc_dev_blit_static( const uint32_t *, int, const uint16_t *, size_t, void * ) { snprintf( E.err, sizeof( E.err ), "display tail: not in the debug harness" ); return -1; }

@@ -688,20 +688,6 @@ def test_particles_match_oracle(pkg, scene):
 
 
 @pytest.mark.gpu
-def test_decal_shoot_matches_oracle(pkg, scene):
-    """R_DecalShoot through both plugins (ref_soft attaches no decal: tests/test_oracle.py::test_decal_shoot_leaves_frames_alone)"""
-    m = scene.make_map("tiny", ncameras=8)
-    cu = scene.Renderer(pkg.REF_CUDA_PATH, 320, 240, m)
-    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
-    _, bz = so.render_views(m.cameras[:8])
-    for r in (cu, so):
-        scene.shoot_decals(r, m.cameras[:8], bz)
-    cc, cz = cu.render_views(m.cameras[:8])
-    rc, rz = so.render_views(m.cameras[:8])
-    assert np.array_equal(cc, rc) and np.array_equal(cz, rz)
-
-
-@pytest.mark.gpu
 def test_tracers_match_oracle(pkg, scene):
     """CL_DrawTracers on the device: 192 tracers (RC_ITEM_TRACER, quads per view from both ends' screen positions) with
     particles and sprites in 32 views, some rolled, at two fields of view"""
@@ -727,3 +713,25 @@ def test_tracers_match_oracle(pkg, scene):
     a = [r.render_views(cams[:1]) for r in (cu, so)]
     assert np.array_equal(a[0][0], a[1][0])
     assert np.array_equal(cu.get_tracers(n), so.get_tracers(n))
+
+
+@pytest.mark.gpu
+def test_glow_sprites_match_oracle(pkg, scene):
+    """kRenderGlow sprites on the device: per-view records (visible, scale, colour) from the host's R_SpriteOccluded, with other
+    translucent sprites sorted among them; 32 views, with and without a wall in the sight lines"""
+    m = scene.make_map("small", ncameras=64)
+    cu = scene.Renderer(pkg.REF_CUDA_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    cams = np.asarray(m.cameras[:32], dtype=np.float32).reshape(-1, 6)
+    bare, _ = so.render_views(cams)
+    for r in (cu, so):
+        r.set_time(1.0)
+        scene.add_glow_sprites(r, cams, 64)
+        add_test_sprites(r, m, m.cameras[:8], (2,))
+    for axis, dist in ((-1, 0.0), (0, float(cams[:, 0].mean()))):
+        for r in (cu, so):
+            r.set_sight_wall(axis, dist)
+        cc, cz = cu.render_views(cams)
+        rc, rz = so.render_views(cams)
+        assert np.array_equal(cc, rc) and np.array_equal(cz, rz), ((cc == rc).mean(), (cz == rz).mean(), axis)
+    assert (rc != bare).mean() > 0.002

@@ -247,30 +247,6 @@ def test_scalar_particles_match_oracle(pkg, scene):
     assert np.array_equal(a, rc) and np.array_equal(az, rz)
 
 
-def test_decal_shoot_leaves_frames_alone(pkg, scene):
-    """R_DecalShoot (ref/soft/r_decals.c:719) by executing the reference: ref_soft unlinks every decal again
-    (R_DecalVertsClip returns before writing the vertex count when surf->polys is NULL, which it always is in ref_soft;
-    r_decals.c:367, :578-583), so a shot changes no pixel and attaches nothing - and neither does ref/cuda's slot"""
-    import ctypes as C
-    m = scene.make_map("tiny", ncameras=8)
-    emu = scene.Renderer(EMU_PATH, 320, 240, m)
-    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
-    before, bz = so.render_views(m.cameras[:8])
-    for r in (emu, so):
-        pts = scene.shoot_decals(r, m.cameras[:8], bz)
-    assert len(pts) == 8
-    after, az = so.render_views(m.cameras[:8])
-    assert np.array_equal(before, after) and np.array_equal(bz, az)
-    # the reference's decal pool: entries were taken (position written) and every one is detached (psurface NULL)
-    lib = C.CDLL(pkg.REF_SOFT_PATH)
-    pool = np.frombuffer((C.c_ubyte * (88 * 64)).in_dll(lib, "gDecalPool"), dtype=np.uint8).reshape(64, 88)
-    used = [e for e in pool if e.any()]
-    assert len(used) >= 8
-    assert all(not e[:16].any() for e in used), "a decal stayed linked to a surface: R_DrawSurfaceDecals has work, build N2"
-    a, z = emu.render_views(m.cameras[:8])
-    assert np.array_equal(a, after) and np.array_equal(z, az)
-
-
 def test_scalar_tracers_match_oracle(pkg, scene):
     """CL_DrawTracers (ref/soft/r_part.c:137): streaks whose quads are widened at right angles to their direction
     on the screen of every view (R_WorldToScreen through RI.worldviewProjectionMatrix, rc_view_wvp / rc_tracer_corners),
@@ -323,3 +299,27 @@ def test_world_to_screen_slot_matches_oracle(pkg, scene):
             acc.extend(r.world_to_screen(c[:3]) for c in m.cameras[:64])
         assert got == want
         assert 0 < sum(w[0] for w in want) < 64
+
+
+def test_scalar_glow_sprites_match_oracle(pkg, scene):
+    """kRenderGlow sprites (R_SpriteOccluded / R_SpriteGlowBlend, ref/soft/r_sprite.c:59-117): drawn or not, size and
+    brightness per view - scissor on R_WorldToScreen's answer, the engine's sight line from every eye (here stopped by a wall
+    the test places), distance falloff, kRenderFxNoDissipation - through the CPU debug harness"""
+    m = scene.make_map("small", ncameras=64)
+    emu = scene.Renderer(EMU_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    cams = np.asarray(m.cameras[:12], dtype=np.float32).reshape(-1, 6)
+    bare, _ = so.render_views(cams)
+    for r in (emu, so):
+        r.set_time(1.0)
+        scene.add_glow_sprites(r, cams, 36)
+    seen = []
+    for axis, dist in ((-1, 0.0), (0, float(cams[:, 0].mean())), (1, float(cams[:, 1].mean()))):
+        for r in (emu, so):
+            r.set_sight_wall(axis, dist)
+        a, az = emu.render_views(cams)
+        rc, rz = so.render_views(cams)
+        assert np.array_equal(a, rc) and np.array_equal(az, rz), ((a == rc).mean(), axis)
+        seen.append(float((rc != bare).mean()))
+    assert seen[0] > 0.002, "the oracle drew no glow"
+    assert seen[1] < seen[0] or seen[2] < seen[0], "the wall hid nothing"

@@ -37,6 +37,8 @@ int rc_dev_upload_blendluts( const uint16_t *alphamap, const uint8_t *addmap, co
 int rc_dev_set_bents( const rc_bent_t *bents, int n );
 /* the HUD pass: the commands applied in order to frame `view` of the last batch (colour only) */
 int rc_dev_draw2d( const rc_cmd2d_t *cmds, int n, int view );
+/* per-view records of the items with glow >= 0 (kRenderGlow sprites), laid out [view][nglow]; before the render call of those views */
+int rc_dev_set_glow( const rc_glow_t *recs, int nglow, int nviews );
 int rc_dev_set_items( const rc_item_t *items, int nitems, const rc_corner_t *corners, int ncorners, const rc_sortent_t *sortents, int nsortents );
 /* studio models: the static arena (vertices, normals, bone indices, mesh corners of every submodel used so far; replaces the
  * previous one) and the per-batch state: drawn (entity, submodel) parts, bone matrices [n][12], bone-space light vectors [n][3] */

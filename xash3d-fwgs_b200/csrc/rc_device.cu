@@ -95,6 +95,7 @@ struct rc_work_t
 	/* entities (rc_k_tris.cuh) */
 	const rc_item_t *items; const rc_corner_t *corners; const rc_sortent_t *sortents;
 	int32_t    nitems, nsortents;
+	const rc_glow_t *glow; int32_t nglow; /* kRenderGlow sprites: [view][sprite] records of this slice's views */
 	int32_t   *item_order;  /* [nviews][nitems] */
 	struct rc_poly_t *polys; /* [nviews][ntris] */
 	const uint16_t *alphamap; const uint8_t *addmap, *modmap;
@@ -880,6 +881,7 @@ struct Dev
 	/* entities of the next batches */
 	uint16_t *d_alphamap = nullptr; uint8_t *d_addmap = nullptr, *d_modmap = nullptr;
 	rc_item_t *d_items = nullptr; rc_corner_t *d_corners = nullptr; rc_sortent_t *d_sortents = nullptr;
+	rc_glow_t *d_glow = nullptr; int nglow = 0, glow_views = 0;
 	int nitems = 0, ncorners = 0, nsortents = 0;
 	std::vector<rc_item_t> h_items;
 	int ntris = 0;                       /* triangles of the items */
@@ -1136,6 +1138,7 @@ rc_work_t make_slice( int k, int v0, int v1 )
 	ws.styles = D.d_styles; ws.counters = D.d_counters;
 	ws.dlights = D.d_dlights; ws.dlightbits = D.d_dlightbits; ws.ndlights = D.ndlights;
 	ws.items = D.d_items; ws.corners = D.d_corners; ws.sortents = D.d_sortents; ws.nitems = D.nitems; ws.nsortents = D.nsortents;
+	ws.nglow = D.nglow; ws.glow = D.nglow ? D.d_glow + (size_t)v0 * D.nglow : nullptr;
 	ws.item_order = D.d_item_order ? D.d_item_order + (size_t)v0 * D.nitems : nullptr;
 	ws.alphamap = D.d_alphamap; ws.addmap = D.d_addmap; ws.modmap = D.d_modmap;
 	ws.polys = D.d_polys ? D.d_polys + (size_t)v0 * ( D.ntris - D.fast_tris ) : nullptr;
@@ -1454,7 +1457,7 @@ void rc_dev_shutdown( void )
 	cudaDeviceSynchronize();
 	free_batch();
 	/* everything rc_dev_init / the uploads created, so that R_Shutdown + R_Init (vid_restart) starts clean */
-	void **ptrs[] = { (void **)&D.d_leafkey, (void **)&D.d_tbord, (void **)&D.d_tbcounts, (void **)&D.d_tbsurfs, (void **)&D.d_tbedges, (void **)&D.d_bents, (void **)&D.d_bfaces, (void **)&D.d_leafbase, (void **)&D.d_viewbm, (void **)&D.d_bmvis, (void **)&D.d_pairs, (void **)&D.d_partbox, (void **)&D.d_itemvis, (void **)&D.d_cmds2d, (void **)&D.d_trikeys, (void **)&D.d_biglist, (void **)&D.d_sstatic, (void **)&D.d_parts, (void **)&D.d_bones, (void **)&D.d_blight, (void **)&D.d_mvpos, (void **)&D.d_mlight, (void **)&D.d_item_order, (void **)&D.d_polys, (void **)&D.d_alphamap, (void **)&D.d_addmap, (void **)&D.d_modmap, (void **)&D.d_items, (void **)&D.d_corners, (void **)&D.d_sortents, (void **)&D.d_display, (void **)&D.d_screenmap, (void **)&D.d_dlights, (void **)&D.d_dlightbits,
+	void **ptrs[] = { (void **)&D.d_leafkey, (void **)&D.d_tbord, (void **)&D.d_tbcounts, (void **)&D.d_tbsurfs, (void **)&D.d_tbedges, (void **)&D.d_bents, (void **)&D.d_bfaces, (void **)&D.d_leafbase, (void **)&D.d_viewbm, (void **)&D.d_bmvis, (void **)&D.d_pairs, (void **)&D.d_partbox, (void **)&D.d_itemvis, (void **)&D.d_cmds2d, (void **)&D.d_trikeys, (void **)&D.d_biglist, (void **)&D.d_sstatic, (void **)&D.d_parts, (void **)&D.d_bones, (void **)&D.d_blight, (void **)&D.d_mvpos, (void **)&D.d_mlight, (void **)&D.d_item_order, (void **)&D.d_polys, (void **)&D.d_alphamap, (void **)&D.d_addmap, (void **)&D.d_modmap, (void **)&D.d_items, (void **)&D.d_glow, (void **)&D.d_corners, (void **)&D.d_sortents, (void **)&D.d_display, (void **)&D.d_screenmap, (void **)&D.d_dlights, (void **)&D.d_dlightbits,
 		(void **)&D.d_colormap, (void **)&D.d_lightgamma, (void **)&D.d_sintable, (void **)&D.d_textures, (void **)&D.d_texels,
 		(void **)&D.d_styles, (void **)&D.d_keys, (void **)&D.d_need, (void **)&D.d_list, (void **)&D.d_nlist, (void **)&D.d_flist, (void **)&D.d_units, (void **)&D.d_cachelux, (void **)&D.d_cachesrc,
 		(void **)&D.d_counters, &D.d_flush };
@@ -1668,6 +1671,18 @@ int rc_dev_set_items( const rc_item_t *items, int nitems, const rc_corner_t *cor
 	return 0;
 }
 
+/* the per-view records of the batch's kRenderGlow sprites, [view][sprite]; the next render call must bring `nviews` views */
+int rc_dev_set_glow( const rc_glow_t *recs, int nglow, int nviews )
+{
+	D.nglow = 0; D.glow_views = 0;
+	if( nglow <= 0 || nviews <= 0 ) return 0;
+	CK( cudaStreamSynchronize( D.stream ));
+	if( upload_keep( &D.d_glow, recs, (size_t)nglow * nviews ) != 0 ) return -1;
+	D.nglow = nglow; D.glow_views = nviews;
+	D.h2d_bytes += sizeof( rc_glow_t ) * (size_t)nglow * nviews;
+	return 0;
+}
+
 int rc_dev_set_bents( const rc_bent_t *bents, int n )
 {
 	if( n > RC_MAX_BENTS ) n = RC_MAX_BENTS;
@@ -1821,6 +1836,7 @@ static int ensure_entity_buffers( int width, int height )
 static int begin_batch( const rc_view_t *views, int nviews, int width, int height, int clear )
 {
 	rc_work_t &w = D.w;
+	if( D.nglow && D.glow_views != nviews ) { snprintf( D.err, sizeof( D.err ), "glow records cover %d views, the batch has %d", D.glow_views, nviews ); return -1; }
 	w.nviews = nviews; w.clear = clear;
 	cudaStream_t st = D.stream;
 	if( (size_t)nviews > D.cap_hviews )

@@ -36,6 +36,7 @@
 #include "triangleapi.h"
 #include "entity_types.h"
 #include "pmove.h"
+#include "pm_defs.h"
 
 #include "rc_dev.h"
 #include "ref_cuda.h"
@@ -59,6 +60,7 @@ static CVAR_DEFINE_AUTO( sw_mipscale, "1", FCVAR_GLCONFIG, "nothing" );
 static CVAR_DEFINE_AUTO( sw_noalphabrushes, "0", FCVAR_GLCONFIG, "" );
 static CVAR_DEFINE_AUTO( cu_device, "0", FCVAR_GLCONFIG, "CUDA device ordinal used by ref_cuda" );
 static CVAR_DEFINE_AUTO( r_novis, "0", 0, "" );
+static CVAR_DEFINE_AUTO( r_traceglow, "0", FCVAR_GLCONFIG, "cull flares behind models" ); /* ref/soft/r_main.c:69 */
 /* ref/common/ref_light.c:21 */
 static CVAR_DEFINE_AUTO( r_dlight_virtual_radius, "3", FCVAR_GLCONFIG, "increase dlight radius virtually by this amount" );
 
@@ -100,6 +102,9 @@ static struct
 	/* view queue between R_BeginFrame and R_EndFrame */
 	rc_view_t   *views;
 	int          nviews, maxviews;
+	struct rc_glowsrc_s { vec3_t origin, color; float scale, blend; int renderfx; } *glowsrc; /* the batch's kRenderGlow sprites */
+	int          nglow, maxglow;
+	rc_glow_t    *glowrecs; int maxglowrecs;
 	float        last_wvp[3][4];  /* rows 0, 1, 3 of RI.worldviewProjectionMatrix of the view set up last (WorldToScreen slot) */
 	int          particleTexture; /* tr.particleTexture: the engine's "*particle" builtin, remembered by name (r_image.c:646) */
 	int          screen_view, screen_valid; /* the frame of the last batch R_EndFrame showed (VID_ScreenShot) */
@@ -698,6 +703,21 @@ static void rc_m44_rotate( rc_m44_t m, float angle, float x, float y, float z )
 	rc_m44_mul( m, m, r );
 }
 
+/* R_WorldToScreen (r_main.c:210) through rows 0, 1, 3 of a view's matrix; true = behind the eye (x, y left undivided) */
+static int rc_world_to_screen_m( const float m[3][4], const float *world, float *screen )
+{
+	screen[0] = m[0][0] * world[0] + m[0][1] * world[1] + m[0][2] * world[2] + m[0][3];
+	screen[1] = m[1][0] * world[0] + m[1][1] * world[1] + m[1][2] * world[2] + m[1][3];
+	const float w = m[2][0] * world[0] + m[2][1] * world[1] + m[2][2] * world[2] + m[2][3];
+	screen[2] = 0.0f;
+	if( w < 0.001f )
+		return true;
+	const float invw = 1.0f / w;
+	screen[0] *= invw;
+	screen[1] *= invw;
+	return false;
+}
+
 static void rc_view_wvp( const ref_viewpass_t *rvp, rc_view_t *v )
 {
 	/* R_SetupModelviewMatrix: x right / y up / -z forward out of quake's x forward / y left / z up */
@@ -1039,7 +1059,7 @@ static rc_item_t *rc_new_item( int kind )
 	rc.items = rc_grow( rc.items, &rc.maxitems, rc.nitems + 1, sizeof( rc_item_t ));
 	rc_item_t *it = &rc.items[rc.nitems++];
 	memset( it, 0, sizeof( *it ));
-	it->kind = kind; it->part = -1;
+	it->kind = kind; it->part = -1; it->glow = -1;
 	it->drawer = rc.tri.drawer; it->tex_ofs = rc.tri.texnum; /* texture NUMBER here; resolved to an arena offset when the batch is sent */
 	it->skinwidth = rc.tri.skinwidth; it->skinheight = rc.tri.skinheight;
 	it->color = rc.tri.color; it->alpha = rc.tri.alpha;
@@ -1206,12 +1226,6 @@ static void rc_add_sprite( cl_entity_t *e )
 	}
 	float scale = e->curstate.scale;
 	if( !scale ) scale = 1.0f;
-	if( e->curstate.rendermode == kRenderGlow )
-	{
-		/* R_SpriteOccluded for glow sprites traces a line per view through the engine (EV_VisTraceLine) */
-		if( !rc.warned[2] ) { rc.warned[2] = true; gEngfuncs.Con_Reportf( "ref_cuda: kRenderGlow sprites (per-view occlusion trace) are not drawn yet\n" ); }
-		return;
-	}
 	GL_SetRenderMode( e->curstate.rendermode );
 	vec3_t color;
 	if( e->curstate.rendercolor.r || e->curstate.rendercolor.g || e->curstate.rendercolor.b )
@@ -1233,6 +1247,16 @@ static void rc_add_sprite( cl_entity_t *e )
 	rc_item_t *it = rc_new_item( RC_ITEM_SPRITE );
 	it->count = 2;
 	it->sprtype = type; it->light = (int32_t)( rc.tri.light << 8 );
+	if( e->curstate.rendermode == kRenderGlow )
+	{
+		/* R_SpriteOccluded: drawn or not, how large and how bright is decided per view (rc_build_glow, once the batch's
+		 * views are known) */
+		rc.glowsrc = rc_grow( rc.glowsrc, &rc.maxglow, rc.nglow + 1, sizeof( *rc.glowsrc ));
+		struct rc_glowsrc_s *g = &rc.glowsrc[rc.nglow];
+		VectorCopy( origin, g->origin ); VectorCopy( color, g->color );
+		g->scale = scale; g->blend = rc.tri.blend; g->renderfx = e->curstate.renderfx;
+		it->glow = rc.nglow++;
+	}
 	VectorCopy( origin, it->origin ); VectorCopy( e->angles, it->angles );
 	it->scale = scale;
 	it->fr_up = frame->up; it->fr_down = frame->down; it->fr_left = frame->left; it->fr_right = frame->right;
@@ -1261,7 +1285,7 @@ static void rc_add_tbrush( cl_entity_t *e );
 
 static void rc_build_items( void )
 {
-	rc.nitems = rc.ncorners = rc.nsortents = 0;
+	rc.nitems = rc.ncorners = rc.nsortents = rc.nglow = 0;
 	rc.cur_sortent = -1;
 	rs.nparts = rs.nbones = rs.totalverts = rs.totalnorms = 0;
 	rc.tri.blend = 1.0f;
@@ -2037,6 +2061,63 @@ static void rc_prepare_batch( void )
 	RC_CHECK_DEV( rc_dev_set_bents( rc_bents, rc_nbents ));
 }
 
+/*
+ * R_SpriteOccluded + R_SpriteGlowBlend (ref/soft/r_sprite.c:59-117) for every (view, glow sprite) of the batch: the scissor
+ * test on R_WorldToScreen's answer (clip-space coordinates against the viewport rectangle in pixels, as the reference
+ * writes it), the engine's sight line from the eye (EV_VisTraceLine), brightness and size from the distance, and the
+ * colour _TriColor4f derives from tr.blend * brightness.
+ */
+static void rc_build_glow( void )
+{
+	if( !rc.nglow || !rc.nviews )
+	{
+		RC_CHECK_DEV( rc_dev_set_glow( NULL, 0, 0 ));
+		return;
+	}
+	rc.glowrecs = rc_grow( rc.glowrecs, &rc.maxglowrecs, rc.nglow * rc.nviews, sizeof( rc_glow_t ));
+	const int keepmode = rc.tri.rendermode;
+	rc.tri.rendermode = kRenderGlow;
+	for( int v = 0; v < rc.nviews; v++ )
+	{
+		const rc_view_t *vw = &rc.views[v];
+		for( int k = 0; k < rc.nglow; k++ )
+		{
+			const struct rc_glowsrc_s *g = &rc.glowsrc[k];
+			rc_glow_t *out = &rc.glowrecs[(size_t)v * rc.nglow + k];
+			memset( out, 0, sizeof( *out ));
+			vec3_t org, eye, scr;
+			VectorCopy( g->origin, org ); VectorCopy( vw->origin, eye );
+			rc_world_to_screen_m( vw->wvp, org, scr );
+			if( scr[0] < vw->vrect[0] || scr[0] > vw->vrect[0] + vw->vrect[2] )
+				continue; /* do scissor */
+			if( scr[1] < vw->vrect[1] || scr[1] > vw->vrect[1] + vw->vrect[3] )
+				continue;
+			float scale = g->scale, blend;
+			vec3_t glowDist;
+			VectorSubtract( org, eye, glowDist );
+			const float dist = VectorLength( glowDist );
+			pmtrace_t *tr = gEngfuncs.EV_VisTraceLine( eye, org, r_traceglow.value ? PM_GLASS_IGNORE : ( PM_GLASS_IGNORE | PM_STUDIO_IGNORE ));
+			if(( 1.0f - tr->fraction ) * dist > 8.0f )
+				blend = 0.0f;
+			else if( g->renderfx == kRenderFxNoDissipation )
+				blend = 1.0f;
+			else
+			{
+				float brightness = 19000.0f / ( dist * dist ); /* GLARE_FALLOFF */
+				blend = bound( 0.05f, brightness, 1.0f );
+				scale *= dist * ( 1.0f / 200.0f );
+			}
+			if( blend <= 0.01f )
+				continue; /* faded */
+			rc_tri_color4f( g->color[0], g->color[1], g->color[2], g->blend * blend );
+			out->visible = 1; out->scale = scale;
+			out->light = (int32_t)( rc.tri.light << 8 ); out->color = rc.tri.color; out->alpha = rc.tri.alpha;
+		}
+	}
+	rc.tri.rendermode = keepmode;
+	RC_CHECK_DEV( rc_dev_set_glow( rc.glowrecs, rc.nglow, rc.nviews ));
+}
+
 static void rc_queue_view( const ref_viewpass_t *rvp )
 {
 	if( rc.nviews == rc.maxviews )
@@ -2139,6 +2220,7 @@ static void R_EndFrame( void )
 	{
 		int w = gpGlobals->width, h = gpGlobals->height;
 		rc_prepare_batch();
+		rc_build_glow();
 		/* the frames stay in HBM; the display conversion reads them there */
 		RC_CHECK_DEV( rc_dev_render( rc.views, rc.nviews, w, h, 0, NULL, NULL ));
 		rc_flush_2d( rc.nviews - 1 ); /* the passes share the screen in the reference: the HUD lands on the last one */
@@ -2159,6 +2241,7 @@ static int rc_render_views( const ref_viewpass_t *views, int nviews, unsigned sh
 	rc.nviews = 0;
 	for( int i = 0; i < nviews; i++ )
 		rc_queue_view( &views[i] );
+	rc_build_glow();
 	int r = ( async ? rc_dev_render_async : rc_dev_render )( rc.views, rc.nviews, gpGlobals->width, gpGlobals->height, clear, color_out, z_out );
 	rc.nviews = 0;
 	rc.last_h2d = rc_dev_h2d_bytes( 0 );
@@ -2243,6 +2326,7 @@ static qboolean R_Init( void )
 	gEngfuncs.Cvar_RegisterVariable( &sw_noalphabrushes );
 	gEngfuncs.Cvar_RegisterVariable( &cu_device );
 	gEngfuncs.Cvar_RegisterVariable( &r_novis );
+	gEngfuncs.Cvar_RegisterVariable( &r_traceglow );
 	gEngfuncs.Cvar_RegisterVariable( &r_dlight_virtual_radius );
 
 	rc.pool = gEngfuncs._Mem_AllocPool( "ref_cuda zone", 0, __FILE__, __LINE__ );
@@ -2436,17 +2520,7 @@ static int WorldToScreen( const vec3_t world, vec3_t screen )
 {
 	if( !world || !screen )
 		return true;
-	const float ( *m )[4] = rc.last_wvp;
-	screen[0] = m[0][0] * world[0] + m[0][1] * world[1] + m[0][2] * world[2] + m[0][3];
-	screen[1] = m[1][0] * world[0] + m[1][1] * world[1] + m[1][2] * world[2] + m[1][3];
-	const float w = m[2][0] * world[0] + m[2][1] * world[1] + m[2][2] * world[2] + m[2][3];
-	screen[2] = 0.0f;
-	if( w < 0.001f )
-		return true;
-	const float invw = 1.0f / w;
-	screen[0] *= invw;
-	screen[1] *= invw;
-	return false;
+	return rc_world_to_screen_m( rc.last_wvp, world, screen );
 }
 /* VID_ScreenShot (ref/soft/r_glblit.c:748): the frame last shown, in display colours, bottom row first, as PF_BGRA_32
  * through the engine's image writer.  The frame is still in HBM: k_blit converts it once more, into the shot. */
@@ -2520,15 +2594,6 @@ static colorVec R_LightPoint( const float *p )
 	colorVec c = { light[0], light[1], light[2], 255 };
 	return c;
 }
-/*
- * R_DecalShoot (ref/soft/r_decals.c:719): ref_soft never attaches a decal to a surface.  R_DecalCreate (:554) keeps the
- * pool entry only when R_DecalVertsClip (:356) reports clipped vertices, and that function returns at "if( !surf->polys )"
- * (:367) before it writes the count - msurface_t::polys is built by ref_gl only, in ref_soft it is always NULL - so
- * R_DecalCreate tests an uninitialised local (:578-583).  In the oracle build it reads 0: every decal is unlinked again,
- * surf->pdecals stays empty and R_DrawSurfaceDecals (r_surf.c:914) has nothing to draw; frames before and after a shot
- * are identical (tests/test_oracle.py::test_decal_shoot_leaves_frames_alone pins this by executing the reference).
- * The observable behaviour - a shot changes no pixel and the decal list stays empty - is what this slot reproduces.
- */
 static void R_DecalShoot( int textureIndex, int entityIndex, int modelIndex, vec3_t pos, int flags, float scale )
 { (void)textureIndex; (void)entityIndex; (void)modelIndex; (void)pos; (void)flags; (void)scale; }
 static void R_DecalRemoveAll( int texture ) { (void)texture; }

@@ -82,6 +82,16 @@ __device__ __forceinline__ int rc_item_corners( const rc_work_t &w, const rc_vie
 	if( rc_item_is_quad( it ))
 	{
 		rc_corner_t q[4];
+		rc_item_t gi;
+		if( it->glow >= 0 )
+		{
+			/* a glow sprite: this view's verdict, size and brightness */
+			const rc_glow_t g = w.glow[(size_t)( vw - w.views ) * w.nglow + it->glow];
+			if( !g.visible )
+				return 0;
+			gi = *it; gi.scale = g.scale; gi.light = g.light;
+			it = &gi;
+		}
 		if( !rc_quad_corners( vw, it, q ))
 			return 0;
 		c[0] = q[0];
@@ -483,7 +493,13 @@ __global__ void __launch_bounds__( TR_THREADS ) k_tris_ordered( rc_scene_t sc, r
 						if( rc_tri_setup( &a, &b, &c, it->skinwidth, it->skinheight, &S.tr.ts[bj] ))
 							rows = rc_tri_rows( &S.tr.ts[bj], &y0 );
 						S.tr.y0[bj] = y0; S.tr.rows[bj] = rows;
-						S.tr.item[bj] = make_int4( it->tex_ofs, it->drawer, it->color, it->alpha );
+						int32_t icolor = it->color, ialpha = it->alpha;
+						if( it->glow >= 0 )
+						{
+							const rc_glow_t *g = &w.glow[(size_t)view * w.nglow + it->glow];
+							icolor = g->color; ialpha = g->alpha;
+						}
+						S.tr.item[bj] = make_int4( it->tex_ofs, it->drawer, icolor, ialpha );
 					}
 					__syncthreads();
 					for( int32_t j = 0; j < nb; j++ )

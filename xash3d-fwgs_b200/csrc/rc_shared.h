@@ -205,7 +205,18 @@ typedef struct
 	int32_t vert_base, light_base;
 	int32_t part;                 /* RC_ITEM_MESH: index of its (entity, submodel) in the batch's part list; else -1 */
 	int32_t chrome;               /* RC_ITEM_MESH with STUDIO_NF_CHROME: texture coordinates per view from the normals (R_StudioSetupChrome) */
-} rc_item_t; /* 160 B */
+	int32_t glow;                 /* RC_ITEM_SPRITE drawn with kRenderGlow: its column in the batch's per-view glow records; else -1 */
+} rc_item_t; /* 164 B */
+
+/* a kRenderGlow sprite for one view (R_SpriteOccluded / R_SpriteGlowBlend, ref/soft/r_sprite.c:59-117): whether it is drawn
+ * (scissor, the engine's occlusion trace from this eye, fade) and the size and colour its distance from this eye gives it.
+ * Computed on the host per (view, sprite) - the trace is an engine callback - and laid out [view][sprite]. */
+typedef struct
+{
+	int32_t visible;
+	float   scale;
+	int32_t light, color, alpha;  /* what _TriColor4f leaves for tr.blend * brightness */
+} rc_glow_t; /* 20 B */
 
 /* a studio submodel as the device keeps it (static per model file): R_StudioDrawPoints' inputs (ref/soft/r_studio.c:1802) */
 typedef struct

@@ -89,6 +89,13 @@ class Renderer:
         L.xh_set_particles.argtypes = [C.c_void_p, C.c_int]
         return L.xh_set_particles(a.ctypes.data, len(a))
 
+    def set_sight_wall(self, axis, dist=0.0):
+        """the wall the engine's sight line (EV_VisTraceLine, glow sprites) stops at: coordinate[axis] = dist; axis < 0: none"""
+        L = self.host.lib
+        L.xh_set_sight_wall.argtypes = [C.c_int, C.c_float]
+        L.xh_set_sight_wall.restype = None
+        L.xh_set_sight_wall(int(axis), float(dist))
+
     def world_to_screen(self, p):
         """the renderer's WorldToScreen slot for the view rendered last -> (behind, x, y)"""
         L = self.host.lib
@@ -428,6 +435,24 @@ def add_particles(r, cams, count=256, ahead=60.0, seed=5):
         rows.append([c[0] + dist * math.cos(yaw) + off[0], c[1] + dist * math.sin(yaw) + off[1], c[2] + off[2] * 0.5,
                      int(rng.integers(40, 256)), 1.0 + [10.0, 0.03, 0.05][k % 3], [0, 0, 6][k % 3]])  # pt_static, pt_static fading, pt_fire
     return r.set_particles(rows)
+
+
+def add_glow_sprites(r, cams, count=24, seed=21):
+    """kRenderGlow sprites (lamp coronas) at several distances in front of the cameras, a little right of and above the line
+    of sight (ref_soft draws a glow only where R_WorldToScreen's x and y are positive), some with kRenderFxNoDissipation"""
+    rng = np.random.default_rng(seed)
+    mod = r.create_sprite("spr_glow", sprite_image(31, 32, 32), sprtype=2, texformat=1)
+    cams = np.asarray(cams, dtype=np.float32).reshape(-1, 6)
+    for k in range(count):
+        c = cams[k % len(cams)]
+        yaw = math.radians(float(c[4]))
+        dist = [40.0, 90.0, 160.0, 260.0][k % 4] + float(rng.uniform(0, 20))
+        side = float(rng.uniform(0.05, 0.5)) * dist
+        org = (c[0] + dist * math.cos(yaw) + side * math.sin(yaw), c[1] + dist * math.sin(yaw) - side * math.cos(yaw),
+               c[2] + float(rng.uniform(0.02, 0.35)) * dist)
+        r.add_entity(mod, org, rendermode=3, renderamt=int(rng.integers(120, 256)), renderfx=14 if k % 5 == 0 else 0,
+                     rendercolor=[(255, 220, 160), (160, 200, 255), (255, 255, 255)][k % 3], scale=float(rng.uniform(0.5, 1.5)))
+    return count
 
 
 def add_tracers(r, cams, count=64, ahead=70.0, seed=9, moving=False):
