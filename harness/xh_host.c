@@ -359,6 +359,11 @@ void xh_decal_shoot( int texture, const float *pos, int flags, float scale )
 	xh.ref.R_DecalShoot( texture, 0, 0, p, flags, scale );
 }
 
+void xh_remove_decals( int texture )
+{
+	xh.ref.R_DecalRemoveAll( texture );
+}
+
 void xh_clear_decals( void )
 {
 	xh.ref.R_ClearAllDecals();

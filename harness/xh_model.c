@@ -530,6 +530,24 @@ int xh_load_map( const void *data, size_t len, const char *name )
 		xh_calc_bounds( mod, out );
 		xh_calc_extents( mod, out );
 
+		/* msurface_t::polys: the face's corners in edge order, as the GL renderers build them for every face
+		 * (ref/gl/gl_rsurf.c GL_BuildPolygonFromSurface; positions only).  ref_soft builds none, and its decal placement
+		 * then decides on an uninitialised count (ref/soft/r_decals.c:367, :578-583): with the polygon in place
+		 * R_DecalVertsClip clips it against the decal as designed, and the oracle's answer is defined. */
+		{
+			glpoly2_t *poly = xh_alloc( sizeof( glpoly2_t ) + sizeof( float ) * VERTEXSIZE * out->numedges );
+			poly->numverts = out->numedges;
+			poly->flags = out->flags;
+			for( int k = 0; k < out->numedges; k++ )
+			{
+				const int e = mod->surfedges[out->firstedge + k];
+				const mvertex_t *v = e >= 0 ? &mod->vertexes[mod->edges16[e].v[0]] : &mod->vertexes[mod->edges16[-e].v[1]];
+				memset( poly->verts[k], 0, sizeof( float ) * VERTEXSIZE );
+				VectorCopy( v->position, poly->verts[k] );
+			}
+			out->polys = poly;
+		}
+
 		if( mod->lightdata && df[i].lightofs != -1 )
 			out->samples = mod->lightdata + df[i].lightofs / 3;
 		if( out->flags & SURF_DRAWTURB )

@@ -33,7 +33,8 @@ struct Emu
 	std::vector<rc_bent_t> bents;
 	std::vector<uint8_t> sstatic; std::vector<rc_spart_t> parts; std::vector<float> bones, blight, mvpos; std::vector<int32_t> mlight;
 	int32_t styles[256];
-	struct Key { int32_t texnum; int32_t light[4]; bool valid; };
+	struct Key { int32_t texnum; int32_t light[4]; bool valid; uint32_t decalgen; };
+	std::vector<rc_ddecal_t> decals; std::vector<int32_t> decal_first; std::vector<uint32_t> decal_gen;
 	std::vector<Key> cachekey;
 	uint64_t counters[RC_CTR_COUNT];
 	std::vector<std::vector<rc_surf_t>> vsurfs; std::vector<std::vector<rc_edge_t>> vedges;
@@ -66,8 +67,20 @@ void build_block( int s, int mip )
 	for( int y = 0; y < h; y++ )
 		for( int x = 0; x < w; x++ )
 			dst[y * w + x] = rc_cache_texel( &E.sc, sf, tex, mip, bl.data(), smax, x, y );
+	if( !E.decal_first.empty() && E.decal_first[2 * s + 1] > 0 )
+	{
+		/* R_DrawSurfaceDecals over the finished block */
+		rc_blendluts_t L = { E.colormap.data(), E.alphamap.data(), E.addmap.data(), E.modmap.data() };
+		const rc_ddecal_t *dl = E.decals.data() + E.decal_first[2 * s];
+		for( int y = 0; y < h; y++ )
+			for( int x = 0; x < w; x++ )
+			{
+				uint32_t px = dst[y * w + x];
+				if( rc_decal_texel( &L, E.texels.data(), dl, E.decal_first[2 * s + 1], mip, x, y, &px )) dst[y * w + x] = (uint16_t)px;
+			}
+	}
 	Emu::Key &k = E.cachekey[s * 4 + mip];
-	k.valid = true; k.texnum = sf->texnum;
+	k.valid = true; k.texnum = sf->texnum; k.decalgen = E.decal_gen.empty() ? 0u : E.decal_gen[s];
 	for( int j = 0; j < 4; j++ ) k.light[j] = sf->styles[j] != 255 ? E.styles[sf->styles[j]] : 0;
 	E.counters[RC_CTR_CACHE_BLOCKS]++; E.counters[RC_CTR_CACHE_TEXELS] += (uint64_t)w * h;
 }
@@ -76,7 +89,7 @@ bool block_stale( int s, int mip )
 {
 	const rc_surface_t *sf = &E.surfaces[s];
 	const Emu::Key &k = E.cachekey[s * 4 + mip];
-	if( !k.valid || k.texnum != sf->texnum ) return true;
+	if( !k.valid || k.texnum != sf->texnum || k.decalgen != ( E.decal_gen.empty() ? 0u : E.decal_gen[s] )) return true;
 	for( int j = 0; j < 4 && sf->styles[j] != 255; j++ )
 		if( k.light[j] != E.styles[sf->styles[j]] ) return true;
 	return false;
@@ -139,6 +152,7 @@ int rc_dev_upload_scene( const rc_scene_t *sc, size_t cache_texels )
 	E.lightdata.assign( sc->lightdata, sc->lightdata + sc->lightdata_len );
 	E.cache.assign( cache_texels, 0 );
 	E.cachekey.assign( (size_t)sc->numsurfaces * 4, Emu::Key{} );
+	E.decals.clear(); E.decal_first.clear(); E.decal_gen.clear();
 	fix_pointers();
 	E.sedgeverts.assign( (size_t)sc->numsurfedges * 6 + 6, 0.0f ); E.sedgepartner.assign( (size_t)sc->numsurfedges + 1, -1 );
 	rc_build_sedge_tables( &E.sc, E.sedgeverts.data(), E.sedgepartner.data());
@@ -643,6 +657,13 @@ int rc_dev_set_dlights( const rc_dlight_t *, int n ) { return n ? -1 : 0; }
 
 /* the display tail is not part of the debug harness (it keeps no frames) */
 int rc_dev_set_screenmap( const uint32_t *, int ) { return 0; }
+int rc_dev_set_decals( const rc_ddecal_t *recs, int nrecs, const int32_t *face_first_count, const uint32_t *face_gen, int nfaces )
+{
+	E.decals.assign( recs, recs + ( nrecs > 0 ? nrecs : 0 ));
+	E.decal_first.assign( face_first_count, face_first_count + 2 * (size_t)nfaces );
+	E.decal_gen.assign( face_gen, face_gen + nfaces );
+	return 0;
+}
 int rc_dev_set_glow( const rc_glow_t *recs, int nglow, int nviews )
 {
 	E.nglow = nglow > 0 ? nglow : 0;

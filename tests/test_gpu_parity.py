@@ -446,7 +446,7 @@ def sprite_image(seed, w=64, h=64):
 def add_test_sprites(r, m, spots, sprtypes=(2,)):
     """sprites of every span drawer next to the given cameras: kRenderNormal (R_PolysetFillSpans8), kRenderTransAdd
     (...Additive), kRenderTransAlpha on an alpha texture (...TextureBlended), kRenderTransTexture (...Blended)"""
-    TF_HAS_ALPHA = 1 << 20
+    TF_HAS_ALPHA = 1 << 16
     mods = {}
     for st in sprtypes:
         mods[st] = [r.create_sprite(f"spr_add{st}", sprite_image(1), sprtype=st, texformat=1),
@@ -539,7 +539,7 @@ def test_light_gamma_change_between_batches(pkg, scene):
 def test_hud_pass_matches_oracle(pkg, scene):
     """R_DrawStretchPic (opaque, alpha-channel, tinted, additive, clipped at every screen border) and
     FillRGBA after the view, through the stock R_BeginFrame .. R_EndFrame loop: the software surfaces are identical."""
-    TF_HAS_ALPHA = 1 << 20
+    TF_HAS_ALPHA = 1 << 16
     m = scene.make_map("small", ncameras=16)
     rs = []
     for path in (pkg.REF_CUDA_PATH, pkg.REF_SOFT_PATH):
@@ -735,3 +735,35 @@ def test_glow_sprites_match_oracle(pkg, scene):
         rc, rz = so.render_views(cams)
         assert np.array_equal(cc, rc) and np.array_equal(cz, rz), ((cc == rc).mean(), (cz == rz).mean(), axis)
     assert (rc != bare).mean() > 0.002
+
+
+@pytest.mark.gpu
+def test_decals_match_oracle(pkg, scene):
+    """N2 decals on the device: faces that carry decals take k_cache_build, which blits them over the finished block
+    (rc_decal_texel); every mip of a face is rebuilt when a decal is hung on it; 40 views, decals at two scales, then removed"""
+    m = scene.make_map("small", ncameras=64)
+    cu = scene.Renderer(pkg.REF_CUDA_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    cams = m.cameras[:16]
+    before, bz = so.render_views(cams)
+    c0, _ = cu.render_views(cams)
+    assert np.array_equal(c0, before)
+    for r in (cu, so):
+        scene.shoot_decals(r, cams, bz)
+        scene.shoot_decals(r, cams[:8], bz, seed=8, scale=2.0)
+    # ref_soft keeps using a block it cached before the shot unless the face is drawn in the very next frame (the shot sets
+    # surf->dlightframe = framecount + 1, r_decals.c:538) or the block is rebuilt for another reason - which of the two depends on
+    # its cache ring's history; ref/cuda rebuilds every block of the face at its next use.  The reference starts from an empty
+    # cache here (R_GammaChanged -> D_FlushCaches) so that both show every decal.
+    so.gamma_changed()
+    rc, rz = so.render_views(m.cameras[:40])
+    cc, cz = cu.render_views(m.cameras[:40])
+    assert (rc[:16] != before).mean() > 0.005
+    assert np.array_equal(cc, rc) and np.array_equal(cz, rz), ((cc == rc).mean(), (cz == rz).mean())
+    for r in (cu, so):
+        r.remove_decals(0)
+        r.host.set_lightstyle(0, "z")
+        r.host.run_lightstyles()
+    rc, rz = so.render_views(cams)
+    cc, cz = cu.render_views(cams)
+    assert np.array_equal(cc, rc) and np.array_equal(cz, rz), ((cc == rc).mean(), (cz == rz).mean())

@@ -323,3 +323,44 @@ def test_scalar_glow_sprites_match_oracle(pkg, scene):
         seen.append(float((rc != bare).mean()))
     assert seen[0] > 0.002, "the oracle drew no glow"
     assert seen[1] < seen[0] or seen[2] < seen[0], "the wall hid nothing"
+
+
+def test_scalar_decals_match_oracle(pkg, scene):
+    """N2 decals (ref/soft/r_decals.c:719 R_DecalShoot, r_surf.c:914 R_DrawSurfaceDecals): decals shot at the walls the
+    views look at - placement over the BSP, the clip of the face polygon against the decal, the blit into every mip of the
+    face's cache blocks with the picture's 3-bit alpha - through the CPU debug harness.  The harness gives the oracle's faces
+    their polygons (xh_model.c), without which ref_soft decides on an uninitialised count.  Pictures with an alpha plane only,
+    as every decal of the game is: for an opaque one R_DrawSurfaceDecals reads `transparent` uninitialised (r_surf.c:932, :985).
+    Scales >= 1 only: the blit ignores the decal's scale, and a decal placed with a smaller one can lie wholly above a face it was
+    hung on, where the reference's unsigned row count wraps (r_surf.c:992-1000) and it runs off the block."""
+    m = scene.make_map("small", ncameras=64)
+    emu = scene.Renderer(EMU_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    cams = m.cameras[:12]
+    before, bz = so.render_views(cams)
+    a0, _ = emu.render_views(cams)
+    assert np.array_equal(a0, before)
+    for r in (emu, so):
+        scene.shoot_decals(r, cams, bz)
+        scene.shoot_decals(r, cams[:8], bz, seed=8, scale=2.0)
+    # ref_soft keeps using a block it cached before the shot unless the face is drawn in the very next frame (the shot sets
+    # surf->dlightframe = framecount + 1, r_decals.c:538) or the block is rebuilt for another reason - which of the two depends on
+    # its cache ring's history; ref/cuda rebuilds every block of the face at its next use.  The reference starts from an empty
+    # cache here (R_GammaChanged -> D_FlushCaches) so that both show every decal.
+    so.gamma_changed()
+    after, az = so.render_views(cams)
+    a, z = emu.render_views(cams)
+    assert (after != before).mean() > 0.005, "the oracle drew no decals"
+    assert np.array_equal(a, after) and np.array_equal(z, az), (a == after).mean()
+    # other mip levels of the same faces: the views from further away / closer
+    a, z = emu.render_views(m.cameras[12:40])
+    rc, rz = so.render_views(m.cameras[12:40])
+    assert np.array_equal(a, rc) and np.array_equal(z, rz), (a == rc).mean()
+    # R_DecalRemoveAll: gone from the lists; blocks built from now on do not carry them
+    for r in (emu, so):
+        r.remove_decals(0)
+        r.host.set_lightstyle(0, "z")
+        r.host.run_lightstyles()
+    a, z = emu.render_views(cams)
+    rc, rz = so.render_views(cams)
+    assert np.array_equal(a, rc) and np.array_equal(z, rz), (a == rc).mean()

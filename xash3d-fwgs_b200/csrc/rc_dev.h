@@ -37,6 +37,9 @@ int rc_dev_upload_blendluts( const uint16_t *alphamap, const uint8_t *addmap, co
 int rc_dev_set_bents( const rc_bent_t *bents, int n );
 /* the HUD pass: the commands applied in order to frame `view` of the last batch (colour only) */
 int rc_dev_draw2d( const rc_cmd2d_t *cmds, int n, int view );
+/* the decals of the world's faces: records grouped by face in list order, per face {first record, count}, per face the
+ * generation its cached blocks must carry (a face whose generation moved is rebuilt at every mip) */
+int rc_dev_set_decals( const rc_ddecal_t *recs, int nrecs, const int32_t *face_first_count, const uint32_t *face_gen, int nfaces );
 /* per-view records of the items with glow >= 0 (kRenderGlow sprites), laid out [view][nglow]; before the render call of those views */
 int rc_dev_set_glow( const rc_glow_t *recs, int nglow, int nviews );
 int rc_dev_set_items( const rc_item_t *items, int nitems, const rc_corner_t *corners, int ncorners, const rc_sortent_t *sortents, int nsortents );

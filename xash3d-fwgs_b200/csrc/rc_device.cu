@@ -30,6 +30,7 @@
 
 #include "rc_dev.h"
 #include "rc_core.h"
+#include "rc_tri.h"
 
 /* ---------------------------------------------------------------------------------------------- */
 /* device-side records private to this file                                                          */
@@ -40,7 +41,7 @@ struct rc_cachekey_t
 	int32_t light[RC_MAXLIGHTMAPS];
 	int32_t valid;
 	int32_t dlight; /* surfcache_t.dlight: built with dynamic lights, never reused (r_surf.c:1099,1149) */
-	int32_t pad;
+	int32_t decalgen; /* the face's decal generation the block was built at (a new decal sets surf->dlightframe: every mip is rebuilt) */
 }; /* 32 B: what D_CacheSurface compares (r_surf.c:1090-1120): texture, light style values */
 
 struct rc_lineinfo_t { int32_t ofs, nsp; }; /* span slice of a scanline: first slot inside the view's arena, count */
@@ -96,6 +97,8 @@ struct rc_work_t
 	const rc_item_t *items; const rc_corner_t *corners; const rc_sortent_t *sortents;
 	int32_t    nitems, nsortents;
 	const rc_glow_t *glow; int32_t nglow; /* kRenderGlow sprites: [view][sprite] records of this slice's views */
+	/* decals (R_DrawSurfaceDecals): records grouped by face, per face {first, count}, per face the generation; null = none */
+	const rc_ddecal_t *decals; const int32_t *decal_first; const uint32_t *decal_gen;
 	int32_t   *item_order;  /* [nviews][nitems] */
 	struct rc_poly_t *polys; /* [nviews][ntris] */
 	const uint16_t *alphamap; const uint8_t *addmap, *modmap;
@@ -364,9 +367,9 @@ __global__ void __launch_bounds__( FC_THREADS ) k_faces_fix( rc_scene_t sc, rc_w
 /* ---------------------------------------------------------------------------------------------- */
 /* S2: surface cache                                                                                 */
 
-__device__ __forceinline__ bool rc_key_stale( const rc_cachekey_t *k, const rc_surface_t *sf, const int32_t *styles )
+__device__ __forceinline__ bool rc_key_stale( const rc_cachekey_t *k, const rc_surface_t *sf, const int32_t *styles, uint32_t decalgen )
 {
-	if( !k->valid || k->texnum != sf->texnum )
+	if( !k->valid || k->texnum != sf->texnum || (uint32_t)k->decalgen != decalgen )
 		return true;
 	for( int j = 0; j < RC_MAXLIGHTMAPS && sf->styles[j] != 255; j++ )
 		if( k->light[j] != styles[sf->styles[j]] )
@@ -404,11 +407,13 @@ __global__ void __launch_bounds__( 256 ) k_cache_list( rc_scene_t sc, rc_work_t 
 	if( sf->cache_ofs[slot & 3] < 0 )
 		return;
 	/* a face lit by a dynamic light is rebuilt every frame, and so is a block that was built with one */
-	if( !( rc_key_stale( &w.cache_keys[slot], sf, w.styles ) || w.cache_keys[slot].dlight || ( w.ndlights && w.dlightbits[slot >> 2] )))
+	const uint32_t decalgen = w.decal_gen ? w.decal_gen[slot >> 2] : 0u;
+	if( !( rc_key_stale( &w.cache_keys[slot], sf, w.styles, decalgen ) || w.cache_keys[slot].dlight || ( w.ndlights && w.dlightbits[slot >> 2] )))
 		return;
 	const rc_cacheitem_t c = rc_cache_item( sf, slot & 3 );
-	if( !c.fast )
+	if( !c.fast || ( w.decal_first && w.decal_first[2 * ( slot >> 2 ) + 1] > 0 ))
 	{
+		/* faces that carry decals take the block-per-item path too: it blits them after the texels */
 		w.cache_list[atomicAdd( w.cache_nlist, 1 )] = slot; /* ragged blocks: k_cache_build, a CTA per item */
 		return;
 	}
@@ -563,6 +568,7 @@ __global__ void __launch_bounds__( 256 ) k_cache_publish( rc_scene_t sc, rc_work
 		for( int j = 0; j < RC_MAXLIGHTMAPS; j++ )
 			kk->light[j] = sf->styles[j] != 255 ? w.styles[sf->styles[j]] : 0;
 		kk->dlight = ( w.ndlights && w.dlightbits[slot >> 2] ) ? 1 : 0;
+		kk->decalgen = (int32_t)( w.decal_gen ? w.decal_gen[slot >> 2] : 0u );
 		kk->valid = 1;
 		texels = (unsigned long long)( sf->lightextents[0] >> mip ) * ( sf->lightextents[1] >> mip );
 	}
@@ -648,12 +654,21 @@ __global__ void __launch_bounds__( CACHE_THREADS ) k_cache_build( rc_scene_t sc,
 		}
 		__syncthreads();
 
-		if( !fast )
+		/* R_DrawSurfaceDecals (r_surf.c:914): the face's decals over the lit texel, in list order, before the one store
+		 * of the texel (another slice may be building the same block at the same time: nothing is read back from it) */
+		const int32_t ndecals = w.decal_first ? w.decal_first[2 * ( slot >> 2 ) + 1] : 0;
+		if( !fast || ndecals > 0 )
 		{
+			const rc_ddecal_t *dl = ndecals > 0 ? w.decals + w.decal_first[2 * ( slot >> 2 )] : nullptr;
+			rc_blendluts_t L;
+			L.colormap = sc.colormap; L.alphamap = w.alphamap; L.addmap = w.addmap; L.modmap = w.modmap;
 			for( int32_t i = tid; i < bw * bh; i += CACHE_THREADS )
 			{
 				int32_t y = i / bw, x = i - y * bw;
-				dst[i] = rc_cache_texel( &sc, sf, tex, mip, s_bl, smax, x, y );
+				uint32_t px = rc_cache_texel( &sc, sf, tex, mip, s_bl, smax, x, y );
+				if( ndecals > 0 )
+					rc_decal_texel( &L, sc.texels, dl, ndecals, mip, x, y, &px );
+				dst[i] = (uint16_t)px;
 			}
 		}
 		else if( mip <= 1 ) rc_cache_runs<8>( sc, tex, mip, s_bl, smax, s_rc, nbu, dst, bw, bh, tid );
@@ -669,6 +684,7 @@ __global__ void __launch_bounds__( CACHE_THREADS ) k_cache_build( rc_scene_t sc,
 			kk->texnum = sf->texnum;
 			for( int j = 0; j < RC_MAXLIGHTMAPS; j++ )
 				kk->light[j] = sf->styles[j] != 255 ? w.styles[sf->styles[j]] : 0;
+			kk->decalgen = (int32_t)( w.decal_gen ? w.decal_gen[slot >> 2] : 0u );
 			kk->valid = 1;
 			kk->dlight = dbits ? 1 : 0;
 			atomicAdd( &w.counters[RC_CTR_CACHE_BLOCKS], 1ull );
@@ -882,6 +898,7 @@ struct Dev
 	uint16_t *d_alphamap = nullptr; uint8_t *d_addmap = nullptr, *d_modmap = nullptr;
 	rc_item_t *d_items = nullptr; rc_corner_t *d_corners = nullptr; rc_sortent_t *d_sortents = nullptr;
 	rc_glow_t *d_glow = nullptr; int nglow = 0, glow_views = 0;
+	rc_ddecal_t *d_decals = nullptr; int32_t *d_decal_first = nullptr; uint32_t *d_decal_gen = nullptr; bool have_decals = false;
 	int nitems = 0, ncorners = 0, nsortents = 0;
 	std::vector<rc_item_t> h_items;
 	int ntris = 0;                       /* triangles of the items */
@@ -1139,6 +1156,7 @@ rc_work_t make_slice( int k, int v0, int v1 )
 	ws.dlights = D.d_dlights; ws.dlightbits = D.d_dlightbits; ws.ndlights = D.ndlights;
 	ws.items = D.d_items; ws.corners = D.d_corners; ws.sortents = D.d_sortents; ws.nitems = D.nitems; ws.nsortents = D.nsortents;
 	ws.nglow = D.nglow; ws.glow = D.nglow ? D.d_glow + (size_t)v0 * D.nglow : nullptr;
+	ws.decals = D.have_decals ? D.d_decals : nullptr; ws.decal_first = D.have_decals ? D.d_decal_first : nullptr; ws.decal_gen = D.have_decals ? D.d_decal_gen : nullptr;
 	ws.item_order = D.d_item_order ? D.d_item_order + (size_t)v0 * D.nitems : nullptr;
 	ws.alphamap = D.d_alphamap; ws.addmap = D.d_addmap; ws.modmap = D.d_modmap;
 	ws.polys = D.d_polys ? D.d_polys + (size_t)v0 * ( D.ntris - D.fast_tris ) : nullptr;
@@ -1457,7 +1475,7 @@ void rc_dev_shutdown( void )
 	cudaDeviceSynchronize();
 	free_batch();
 	/* everything rc_dev_init / the uploads created, so that R_Shutdown + R_Init (vid_restart) starts clean */
-	void **ptrs[] = { (void **)&D.d_leafkey, (void **)&D.d_tbord, (void **)&D.d_tbcounts, (void **)&D.d_tbsurfs, (void **)&D.d_tbedges, (void **)&D.d_bents, (void **)&D.d_bfaces, (void **)&D.d_leafbase, (void **)&D.d_viewbm, (void **)&D.d_bmvis, (void **)&D.d_pairs, (void **)&D.d_partbox, (void **)&D.d_itemvis, (void **)&D.d_cmds2d, (void **)&D.d_trikeys, (void **)&D.d_biglist, (void **)&D.d_sstatic, (void **)&D.d_parts, (void **)&D.d_bones, (void **)&D.d_blight, (void **)&D.d_mvpos, (void **)&D.d_mlight, (void **)&D.d_item_order, (void **)&D.d_polys, (void **)&D.d_alphamap, (void **)&D.d_addmap, (void **)&D.d_modmap, (void **)&D.d_items, (void **)&D.d_glow, (void **)&D.d_corners, (void **)&D.d_sortents, (void **)&D.d_display, (void **)&D.d_screenmap, (void **)&D.d_dlights, (void **)&D.d_dlightbits,
+	void **ptrs[] = { (void **)&D.d_leafkey, (void **)&D.d_tbord, (void **)&D.d_tbcounts, (void **)&D.d_tbsurfs, (void **)&D.d_tbedges, (void **)&D.d_bents, (void **)&D.d_bfaces, (void **)&D.d_leafbase, (void **)&D.d_viewbm, (void **)&D.d_bmvis, (void **)&D.d_pairs, (void **)&D.d_partbox, (void **)&D.d_itemvis, (void **)&D.d_cmds2d, (void **)&D.d_trikeys, (void **)&D.d_biglist, (void **)&D.d_sstatic, (void **)&D.d_parts, (void **)&D.d_bones, (void **)&D.d_blight, (void **)&D.d_mvpos, (void **)&D.d_mlight, (void **)&D.d_item_order, (void **)&D.d_polys, (void **)&D.d_alphamap, (void **)&D.d_addmap, (void **)&D.d_modmap, (void **)&D.d_items, (void **)&D.d_glow, (void **)&D.d_decals, (void **)&D.d_decal_first, (void **)&D.d_decal_gen, (void **)&D.d_corners, (void **)&D.d_sortents, (void **)&D.d_display, (void **)&D.d_screenmap, (void **)&D.d_dlights, (void **)&D.d_dlightbits,
 		(void **)&D.d_colormap, (void **)&D.d_lightgamma, (void **)&D.d_sintable, (void **)&D.d_textures, (void **)&D.d_texels,
 		(void **)&D.d_styles, (void **)&D.d_keys, (void **)&D.d_need, (void **)&D.d_list, (void **)&D.d_nlist, (void **)&D.d_flist, (void **)&D.d_units, (void **)&D.d_cachelux, (void **)&D.d_cachesrc,
 		(void **)&D.d_counters, &D.d_flush };
@@ -1629,6 +1647,7 @@ int rc_dev_upload_scene( const rc_scene_t *sc, size_t cache_texels )
 	D.sc = d;
 	D.cache_texels = cache_texels;
 	D.h_surfaces.assign( sc->surfaces, sc->surfaces + sc->numsurfaces );
+	D.have_decals = false; /* the tables are per face of the previous world */
 
 	size_t nslots = (size_t)sc->numsurfaces * 4;
 	if( upload( &D.d_keys, (const rc_cachekey_t *)nullptr, nslots ) != 0 ) return -1;
@@ -1668,6 +1687,19 @@ int rc_dev_set_items( const rc_item_t *items, int nitems, const rc_corner_t *cor
 	D.fast_maxcount = 0;
 	for( int i = 0; i < D.nfast_items; i++ ) if( items[i].count > D.fast_maxcount ) D.fast_maxcount = items[i].count;
 	D.h2d_bytes += sizeof( rc_item_t ) * (size_t)nitems + sizeof( rc_corner_t ) * (size_t)ncorners + sizeof( rc_sortent_t ) * (size_t)nsortents;
+	return 0;
+}
+
+int rc_dev_set_decals( const rc_ddecal_t *recs, int nrecs, const int32_t *face_first_count, const uint32_t *face_gen, int nfaces )
+{
+	if( nfaces != D.sc.numsurfaces ) { snprintf( D.err, sizeof( D.err ), "decal tables for %d faces, the world has %d", nfaces, D.sc.numsurfaces ); return -1; }
+	if( rc_dev_wait() != 0 ) return -1;
+	CK( cudaDeviceSynchronize());
+	if( upload_keep( &D.d_decals, recs, (size_t)( nrecs > 0 ? nrecs : 1 )) != 0 ) return -1;
+	if( upload_keep( &D.d_decal_first, face_first_count, (size_t)nfaces * 2 ) != 0 ) return -1;
+	if( upload_keep( &D.d_decal_gen, face_gen, (size_t)nfaces ) != 0 ) return -1;
+	D.have_decals = true;
+	D.h2d_bytes += sizeof( rc_ddecal_t ) * (size_t)nrecs + 12 * (size_t)nfaces;
 	return 0;
 }
 

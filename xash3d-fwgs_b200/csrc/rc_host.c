@@ -37,6 +37,7 @@
 #include "entity_types.h"
 #include "pmove.h"
 #include "pm_defs.h"
+#include "protocol.h"
 
 #include "rc_dev.h"
 #include "ref_cuda.h"
@@ -103,9 +104,10 @@ static struct
 	rc_view_t   *views;
 	int          nviews, maxviews;
 	struct rc_glowsrc_s { vec3_t origin, color; float scale, blend; int renderfx; } *glowsrc; /* the batch's kRenderGlow sprites */
-	int          nglow, maxglow;
+	int          nglow, maxglow, ntracers;
 	rc_glow_t    *glowrecs; int maxglowrecs;
-	float        last_wvp[3][4];  /* rows 0, 1, 3 of RI.worldviewProjectionMatrix of the view set up last (WorldToScreen slot) */
+	ref_viewpass_t last_rvp;      /* the view set up last: the WorldToScreen slot answers for it */
+	qboolean     batch_wvp;       /* the batch draws tracers or glow sprites: its views carry RI.worldviewProjectionMatrix */
 	int          particleTexture; /* tr.particleTexture: the engine's "*particle" builtin, remembered by name (r_image.c:646) */
 	int          screen_view, screen_valid; /* the frame of the last batch R_EndFrame showed (VID_ScreenShot) */
 	rc_cmd2d_t  *cmds2d; int ncmds2d, maxcmds2d; /* the frame's HUD pass (R_DrawStretchPic / FillRGBA), applied in R_EndFrame */
@@ -360,10 +362,12 @@ static void GL_FreeTexture( unsigned int texnum )
 
 /* lay out the pixel_t arena (four mips + alpha plane per live texture), gather the RGBA sources in one upload arena and let
  * the device encode them */
+static void rc_decals_texels_moved( void );
 static void rc_sync_textures( void )
 {
 	if( !rc.textures_dirty )
 		return;
+	rc_decals_texels_moved(); /* decal records hold texel arena offsets */
 	const int n = rc.numImages;
 	rc_free( rc.textab );
 	rc_texture_t *tab = rc.textab = rc_malloc( sizeof( rc_texture_t ) * Q_max( 1, n ));
@@ -468,10 +472,12 @@ static void rc_resolve_texnums( qboolean force )
 		RC_CHECK_DEV( rc_dev_update_surface_texnums( rc.surf_texnum, w->numsurfaces ));
 }
 
+static void rc_clear_decals( void );
 static void R_NewMap( void )
 {
 	model_t *w = gp_cl->models[1];
 	rc.world = w;
+	rc_clear_decals(); /* R_ClearDecals, r_main.c:1234 */
 	rc.scene_valid = false;
 	if( !w )
 		return;
@@ -859,8 +865,10 @@ static void rc_setup_view( const ref_viewpass_t *rvp, rc_view_t *v )
 	v->texfilt = sw_texfilt.value == 1.0f;
 	v->flags = rvp->flags;
 	v->pvs_radius = r_novis.value ? -1.0f : r_pvs_radius->value;
-	rc_view_wvp( rvp, v );
-	memcpy( rc.last_wvp, v->wvp, sizeof( rc.last_wvp ));
+	/* R_WorldToScreen's matrix: three rotations and two tangents per view, only for batches that ask for it */
+	if( rc.batch_wvp )
+		rc_view_wvp( rvp, v );
+	rc.last_rvp = *rvp;
 }
 
 /* ---------------------------------------------------------------------------------------------- */
@@ -1285,7 +1293,7 @@ static void rc_add_tbrush( cl_entity_t *e );
 
 static void rc_build_items( void )
 {
-	rc.nitems = rc.ncorners = rc.nsortents = rc.nglow = 0;
+	rc.nitems = rc.ncorners = rc.nsortents = rc.nglow = rc.ntracers = 0;
 	rc.cur_sortent = -1;
 	rs.nparts = rs.nbones = rs.totalverts = rs.totalnorms = 0;
 	rc.tri.blend = 1.0f;
@@ -2047,6 +2055,7 @@ static void rc_sync_lightgamma( void )
 	RC_CHECK_DEV( rc_dev_flush_cache());
 }
 
+static void rc_send_decals( void );
 static void rc_prepare_batch( void )
 {
 	if( !rc.scene_valid )
@@ -2054,6 +2063,7 @@ static void rc_prepare_batch( void )
 	rc_sync_lightgamma();
 	rc_sync_textures();
 	rc_resolve_texnums( false );
+	rc_send_decals();
 	RC_CHECK_DEV( rc_dev_set_lightstyles( rc.lightstylevalue ));
 	rc_push_dlights();
 	rc_build_bents();
@@ -2131,7 +2141,13 @@ static void rc_queue_view( const ref_viewpass_t *rvp )
 
 static void R_Set2DMode( qboolean enable );
 static void rc_flush_2d( int view );
-static void R_BeginFrame( qboolean clearScene ) { (void)clearScene; rc.nviews = 0; rc.ncmds2d = 0; R_Set2DMode( true ); }
+static void R_BeginFrame( qboolean clearScene )
+{
+	(void)clearScene;
+	rc.nviews = 0; rc.ncmds2d = 0;
+	rc.batch_wvp = true; /* the frame's views are set up before its entities are known */
+	R_Set2DMode( true );
+}
 
 /* GL_RenderFrame slot == R_RenderFrame (ref/soft/r_main.c:1141): here the view is only recorded */
 static void R_RenderFrame( const ref_viewpass_t *rvp )
@@ -2239,6 +2255,7 @@ static int rc_render_views( const ref_viewpass_t *views, int nviews, unsigned sh
 	rc_dev_h2d_bytes( 1 );
 	rc_prepare_batch();
 	rc.nviews = 0;
+	rc.batch_wvp = rc.nglow > 0 || rc.ntracers > 0;
 	for( int i = 0; i < nviews; i++ )
 		rc_queue_view( &views[i] );
 	rc_build_glow();
@@ -2520,7 +2537,9 @@ static int WorldToScreen( const vec3_t world, vec3_t screen )
 {
 	if( !world || !screen )
 		return true;
-	return rc_world_to_screen_m( rc.last_wvp, world, screen );
+	rc_view_t v;
+	rc_view_wvp( &rc.last_rvp, &v );
+	return rc_world_to_screen_m( v.wvp, world, screen );
 }
 /* VID_ScreenShot (ref/soft/r_glblit.c:748): the frame last shown, in display colours, bottom row first, as PF_BGRA_32
  * through the engine's image writer.  The frame is still in HBM: k_blit converts it once more, into the shot. */
@@ -2594,11 +2613,490 @@ static colorVec R_LightPoint( const float *p )
 	colorVec c = { light[0], light[1], light[2], 255 };
 	return c;
 }
+/* ---------------------------------------------------------------------------------------------- */
+/*
+ * N2 decals: placement (ref/soft/r_decals.c) on the host, drawing into the surface cache (R_DrawSurfaceDecals,
+ * r_surf.c:914) on the device.  A decal is a decal_t of the engine's ABI hung on msurface_t::pdecals, as in every
+ * renderer of the tree (the engine's save / restore walks those lists).
+ *
+ * ref_soft keeps a new decal only when R_DecalVertsClip reports that the face's polygon, clipped to the decal's unit
+ * square in decal texture space, has vertices left (r_decals.c:356, :578).  It reads the polygon from msurface_t::polys,
+ * which only the GL renderers build: in ref_soft the pointer is NULL, the function returns before it writes the count
+ * and R_DecalCreate tests an uninitialised local.  ref/cuda takes the designed path - it clips the polygon it reads from
+ * the BSP's own edges - and the test harness gives the oracle's faces their polygons so that the reference takes it too.
+ */
+#define RC_DECAL_DISTANCE   4
+#define RC_MAX_OVERLAP      6     /* MAX_OVERLAP_DECALS */
+#define RC_DECAL_CLIPVERTS  32    /* MAX_DECALCLIPVERT */
+
+static decal_t rc_decal_pool[MAX_RENDER_DECALS];
+static int     rc_decal_next;
+static qboolean rc_decals_dirty; /* the device's decal lists are out of date */
+static uint32_t *rc_decal_gen;   /* per world face: bumped when a decal is hung on it (forces the rebuild of its cache blocks) */
+static int      rc_decal_gen_n;
+
+typedef struct
+{
+	vec3_t  position;
+	model_t *model;
+	int     texture, size, flags, entity;
+	float   scale;
+	int     width, height;   /* world size of the picture */
+	vec3_t  basis[3];
+} rc_decalshot_t;
+
+static void rc_decals_texels_moved( void ) { rc_decals_dirty = true; }
+
+static void rc_decal_gen_ensure( void )
+{
+	if( rc.world && rc_decal_gen_n != rc.world->numsurfaces )
+	{
+		rc_free( rc_decal_gen );
+		rc_decal_gen_n = rc.world->numsurfaces;
+		rc_decal_gen = rc_malloc( sizeof( uint32_t ) * Q_max( 1, rc_decal_gen_n ));
+		memset( rc_decal_gen, 0, sizeof( uint32_t ) * Q_max( 1, rc_decal_gen_n ));
+	}
+}
+
+static void rc_decal_gen_bump( msurface_t *surf )
+{
+	if( !rc.world )
+		return;
+	rc_decal_gen_ensure();
+	const int i = (int)( surf - rc.world->surfaces );
+	if( i >= 0 && i < rc_decal_gen_n )
+		rc_decal_gen[i]++;
+	rc_decals_dirty = true;
+}
+
+static void rc_decal_unlink( decal_t *d )
+{
+	msurface_t *surf = d->psurface;
+	if( surf )
+	{
+		decal_t **link = &surf->pdecals;
+		while( *link && *link != d )
+			link = &( *link )->pnext;
+		if( *link == d )
+			*link = d->pnext;
+		rc_decals_dirty = true; /* the lists changed; the face's cached blocks stay as they are, as in the reference */
+	}
+	d->psurface = NULL;
+	d->polys = NULL;
+}
+
+/* R_DecalAlloc: the entry to overwrite - the one handed in, or the next of the ring that is not permanent */
+static decal_t *rc_decal_alloc( decal_t *d )
+{
+	int limit = MAX_RENDER_DECALS;
+	if( r_decals->value < limit )
+		limit = r_decals->value;
+	if( !limit )
+		return NULL;
+	if( !d )
+	{
+		int count = 0;
+		do
+		{
+			if( rc_decal_next >= limit )
+				rc_decal_next = 0;
+			d = &rc_decal_pool[rc_decal_next++];
+			count++;
+		} while( FBitSet( d->flags, FDECAL_PERMANENT ) && count < limit );
+	}
+	rc_decal_unlink( d );
+	return d;
+}
+
+/* R_DecalComputeBasis: the face's texture axes and normal, unit length */
+static void rc_decal_basis( const msurface_t *surf, vec3_t basis[3] )
+{
+	vec3_t n;
+	if( surf->flags & SURF_PLANEBACK ) VectorNegate( surf->plane->normal, n );
+	else VectorCopy( surf->plane->normal, n );
+	VectorNormalize2( n, basis[2] );
+	VectorNormalize2( surf->texinfo->vecs[0], basis[0] );
+	VectorNormalize2( surf->texinfo->vecs[1], basis[1] );
+}
+
+/* R_SetupDecalTextureSpaceBasis: world -> decal texture space ([0,1] over the picture) */
+static void rc_decal_texbasis( const decal_t *d, const msurface_t *surf, int texture, vec3_t basis[3], float worldscale[2] )
+{
+	rc_decal_basis( surf, basis );
+	const rc_image_t *img = &rc.images[( texture >= 0 && texture < RC_MAX_TEXTURES ) ? texture : 0];
+	int width = 1, height = 1; /* R_GetDecalDimensions */
+	width = img->srcWidth; height = img->srcHeight;
+	worldscale[0] = (float)d->scale / width;
+	worldscale[1] = (float)d->scale / height;
+	VectorScale( basis[0], worldscale[0], basis[0] );
+	VectorScale( basis[1], worldscale[1], basis[1] );
+}
+
+/* one pass of the Sutherland-Hodgman clip (SHClip, r_decals.c:292) over decal-space (u, v) pairs */
+static int rc_decal_clip_edge( const float ( *in )[2], int n, float ( *out )[2], int edge )
+{
+	int m = 0;
+	const int axis = edge >> 1;            /* 0: u (left, right), 1: v (top, bottom) */
+	const float lim = ( edge & 1 ) ? 1.0f : 0.0f;
+#define RC_INSIDE( p ) (( edge & 1 ) ? ( p )[axis] < 1.0f : ( p )[axis] > 0.0f )
+	const float *s = in[n - 1];
+	for( int j = 0; j < n; j++ )
+	{
+		const float *p = in[j];
+		const qboolean pin = RC_INSIDE( p ), sin_ = RC_INSIDE( s );
+		if( pin != sin_ )
+		{
+			/* R_ClipIntersect( one, two ): entering: one = s, two = p; leaving: one = p, two = s */
+			const float *one = pin ? s : p, *two = pin ? p : s;
+			const float t = (( one[axis] - lim ) / ( one[axis] - two[axis] ));
+			if( m < RC_DECAL_CLIPVERTS )
+			{
+				out[m][axis] = lim;
+				out[m][axis ^ 1] = one[axis ^ 1] + ( two[axis ^ 1] - one[axis ^ 1] ) * t;
+				m++;
+			}
+		}
+		if( pin && m < RC_DECAL_CLIPVERTS )
+		{
+			out[m][0] = p[0]; out[m][1] = p[1];
+			m++;
+		}
+		s = p;
+	}
+#undef RC_INSIDE
+	return m;
+}
+
+/* R_DecalVertsClip: sets the decal's dx, dy (R_SetupDecalClip) and counts what is left of the face's polygon inside
+ * the decal's square */
+static int rc_decal_clip_face( decal_t *d, const msurface_t *surf, const model_t *mod, int texture )
+{
+	vec3_t basis[3];
+	float worldscale[2];
+	rc_decal_texbasis( d, surf, texture, basis, worldscale );
+	d->dx = DotProduct( d->position, basis[0] );
+	d->dy = DotProduct( d->position, basis[1] );
+	float a[RC_DECAL_CLIPVERTS][2], b[RC_DECAL_CLIPVERTS][2];
+	int n = 0;
+	for( int i = 0; i < surf->numedges && n < RC_DECAL_CLIPVERTS; i++ )
+	{
+		const int e = mod->surfedges[surf->firstedge + i];
+		const float *v;
+		if( FBitSet( mod->flags, MODEL_QBSP2 )) v = e >= 0 ? mod->vertexes[mod->edges32[e].v[0]].position : mod->vertexes[mod->edges32[-e].v[1]].position;
+		else v = e >= 0 ? mod->vertexes[mod->edges16[e].v[0]].position : mod->vertexes[mod->edges16[-e].v[1]].position;
+		a[n][0] = DotProduct( v, basis[0] ) - d->dx + 0.5f;
+		a[n][1] = DotProduct( v, basis[1] ) - d->dy + 0.5f;
+		n++;
+	}
+	if( !n )
+		return 0;
+	n = rc_decal_clip_edge( a, n, b, 0 );
+	if( n ) n = rc_decal_clip_edge( b, n, a, 1 );
+	if( n ) n = rc_decal_clip_edge( a, n, b, 2 );
+	if( n ) n = rc_decal_clip_edge( b, n, a, 3 );
+	return n;
+}
+
+/* R_DecalIntersect: how many decals of the face the new one would mostly cover, and the smallest of them */
+static decal_t *rc_decal_intersect( const rc_decalshot_t *shot, msurface_t *surf, int *pcount )
+{
+	decal_t *last = NULL;
+	float lastarea = 2;
+	vec3_t ext[2];
+	const rc_image_t *img = &rc.images[shot->texture];
+	*pcount = 0;
+	VectorScale( shot->basis[0], (( img->srcWidth / shot->scale ) * 0.5f ), ext[0] );
+	VectorScale( shot->basis[1], (( img->srcHeight / shot->scale ) * 0.5f ), ext[1] );
+	for( decal_t *d = surf->pdecals; d; d = d->pnext )
+	{
+		if( !FBitSet( d->flags, FDECAL_PERMANENT ))
+		{
+			vec3_t tb[3], tp[2];
+			float ws[2];
+			rc_decal_texbasis( d, surf, d->texture, tb, ws );
+			VectorSubtract( shot->position, ext[0], tp[0] );
+			VectorSubtract( shot->position, ext[1], tp[1] );
+			const float minx = DotProduct( tp[0], tb[0] ) - d->dx + 0.5f, miny = DotProduct( tp[1], tb[1] ) - d->dy + 0.5f;
+			VectorAdd( shot->position, ext[0], tp[0] );
+			VectorAdd( shot->position, ext[1], tp[1] );
+			const float maxx = DotProduct( tp[0], tb[0] ) - d->dx + 0.5f, maxy = DotProduct( tp[1], tb[1] ) - d->dy + 0.5f;
+			const float umin[2] = { Q_max( minx, 0 ), Q_max( miny, 0 ) }, umax[2] = { Q_min( maxx, 1 ), Q_min( maxy, 1 ) };
+			if( umin[0] < 1 && umin[1] < 1 && umax[0] > 0 && umax[1] > 0 )
+			{
+				/* the reference's expression, umin[1] in the first factor included */
+				const float area = ( umax[0] - umin[1] ) * ( umax[1] - umin[1] );
+				if( area > 0.6f )
+				{
+					*pcount += 1;
+					if( !last || area <= lastarea ) { last = d; lastarea = area; }
+				}
+			}
+		}
+		if( d == d->pnext ) break;
+	}
+	return last;
+}
+
+/* R_DecalCreate + R_AddDecalToSurface */
+static void rc_decal_create( const rc_decalshot_t *shot, msurface_t *surf, float x, float y )
+{
+	int count;
+	decal_t *old = rc_decal_intersect( shot, surf, &count );
+	if( count < RC_MAX_OVERLAP )
+		old = NULL;
+	decal_t *d = rc_decal_alloc( old );
+	if( !d )
+		return;
+	d->flags = shot->flags;
+	VectorCopy( shot->position, d->position );
+	d->dx = x; d->dy = y;
+	d->scale = shot->scale;
+	d->entityIndex = shot->entity;
+	d->texture = shot->texture;
+	if( !rc_decal_clip_face( d, surf, shot->model, shot->texture ))
+	{
+		rc_decal_unlink( d );
+		return;
+	}
+	d->pnext = NULL;
+	decal_t *tail = surf->pdecals;
+	if( tail )
+	{
+		while( tail->pnext && tail != tail->pnext )
+			tail = tail->pnext;
+		tail->pnext = d;
+	}
+	else surf->pdecals = d;
+	d->psurface = surf;
+	rc_decal_gen_bump( surf ); /* surf->dlightframe = tr.framecount + 1: every cached block of the face is rebuilt */
+}
+
+/* R_DecalSurface: does the picture's rectangle touch the face */
+static void rc_decal_surface( msurface_t *surf, rc_decalshot_t *shot )
+{
+	const mtexinfo_t *tex = surf->texinfo;
+	const connstate_t state = (connstate_t)gEngfuncs.EngineGetParm( PARM_CONNSTATE, 0 );
+	if( state == ca_connected || state == ca_validate )
+	{
+		/* restoring a level: a decal that came over from the neighbouring one is not placed twice */
+		for( decal_t *d = surf->pdecals; d && d != d->pnext; d = d->pnext )
+			if( VectorCompare( d->position, shot->position ) && d->texture == shot->texture )
+				return;
+	}
+	float s = DotProduct( shot->position, tex->vecs[0] ) + tex->vecs[0][3] - surf->texturemins[0];
+	float t = DotProduct( shot->position, tex->vecs[1] ) + tex->vecs[1][3] - surf->texturemins[1];
+	rc_decal_basis( surf, shot->basis );
+	const float w = fabs( shot->width * DotProduct( tex->vecs[0], shot->basis[0] )) + fabs( shot->height * DotProduct( tex->vecs[0], shot->basis[1] ));
+	const float h = fabs( shot->width * DotProduct( tex->vecs[1], shot->basis[0] )) + fabs( shot->height * DotProduct( tex->vecs[1], shot->basis[1] ));
+	s -= ( w * 0.5f );
+	t -= ( h * 0.5f );
+	if( s <= -w || t <= -h || s > ( surf->extents[0] + w ) || t > ( surf->extents[1] + h ))
+		return;
+	rc_decal_create( shot, surf, s, t );
+}
+
+/* R_DecalNode: the nodes whose plane passes within the picture's size of the point */
+static void rc_decal_node( model_t *model, mnode_t *node, rc_decalshot_t *shot )
+{
+	while( node->contents >= 0 )
+	{
+		const mplane_t *plane = node->plane;
+		const float dist = DotProduct( shot->position, plane->normal ) - plane->dist;
+		if( dist > shot->size ) { node = node_child( node, 0, model ); continue; }
+		if( dist < -shot->size ) { node = node_child( node, 1, model ); continue; }
+		if( dist < RC_DECAL_DISTANCE && dist > -RC_DECAL_DISTANCE )
+		{
+			msurface_t *surf = model->surfaces + node_firstsurface( node, model );
+			for( int i = 0, n = node_numsurfaces( node, model ); i < n; i++, surf++ )
+				if( !( surf->flags & ( SURF_DRAWTURB | SURF_DRAWSKY | SURF_CONVEYOR )))
+					rc_decal_surface( surf, shot );
+		}
+		rc_decal_node( model, node_child( node, 0, model ), shot );
+		node = node_child( node, 1, model );
+	}
+}
+
+/* CL_ModelHandle (r_local.h:505) */
+static model_t *rc_model_handle( int index )
+{
+	return ( index >= 0 && index < gp_cl->nummodels ) ? gp_cl->models[index] : NULL;
+}
+
+/* R_DecalShoot (ref/soft/r_decals.c:719) */
 static void R_DecalShoot( int textureIndex, int entityIndex, int modelIndex, vec3_t pos, int flags, float scale )
-{ (void)textureIndex; (void)entityIndex; (void)modelIndex; (void)pos; (void)flags; (void)scale; }
-static void R_DecalRemoveAll( int texture ) { (void)texture; }
-static int R_CreateDecalList( struct decallist_s *pList ) { (void)pList; return 0; }
-static void R_ClearAllDecals( void ) {}
+{
+	rc_decalshot_t shot;
+	cl_entity_t *ent = NULL;
+	model_t *model = NULL;
+	if( textureIndex <= 0 || textureIndex >= RC_MAX_TEXTURES )
+	{
+		gEngfuncs.Con_Printf( S_ERROR "Decal has invalid texture!\n" );
+		return;
+	}
+	if( entityIndex > 0 )
+	{
+		ent = ( rc.entities && (uint)entityIndex < rc.max_entities ) ? &rc.entities[entityIndex] : NULL;
+		if( modelIndex > 0 ) model = rc_model_handle( modelIndex );
+		else if( ent != NULL ) model = rc_model_handle( ent->curstate.modelindex );
+		else return;
+	}
+	else if( modelIndex > 0 ) model = rc_model_handle( modelIndex );
+	else model = gp_cl->models[1];
+	if( !model )
+		return;
+	if( model->type != mod_brush )
+	{
+		gEngfuncs.Con_Reportf( S_ERROR "Decals must hit mod_brush!\n" );
+		return;
+	}
+	memset( &shot, 0, sizeof( shot ));
+	shot.model = model;
+	const hull_t *hull = &model->hulls[0];
+	if( ent && !FBitSet( flags, FDECAL_LOCAL_SPACE ))
+	{
+		/* into the brush entity's own space */
+		vec3_t local;
+		if( !VectorIsNull( ent->angles ))
+		{
+			matrix4x4 m;
+			Matrix4x4_CreateFromEntity( m, ent->angles, ent->origin, 1.0f );
+			Matrix4x4_VectorITransform( m, pos, local );
+		}
+		else VectorSubtract( pos, ent->origin, local );
+		VectorCopy( local, shot.position );
+		SetBits( flags, FDECAL_LOCAL_SPACE );
+	}
+	else VectorCopy( pos, shot.position );
+	if( !FBitSet( model->flags, MODEL_HAS_ORIGIN ))
+		SetBits( flags, FDECAL_USE_LANDMARK );
+	shot.texture = textureIndex;
+	shot.entity = entityIndex;
+	shot.flags = flags;
+	const int width = rc.images[textureIndex].srcWidth, height = rc.images[textureIndex].srcHeight;
+	shot.size = width >> 1;
+	if(( height >> 1 ) > shot.size )
+		shot.size = height >> 1;
+	shot.scale = bound( 0.01f, scale, 16.0f ); /* MIN_DECAL_SCALE, MAX_DECAL_SCALE */
+	shot.width = width / shot.scale;
+	shot.height = height / shot.scale;
+	rc_decal_node( model, &model->nodes[hull->firstclipnode], &shot );
+}
+
+/* R_DecalRemoveAll (r_decals.c:978): the decals of one texture (0: of any) among the pool entries handed out so far */
+static void R_DecalRemoveAll( int texture )
+{
+	if( texture < 0 || texture >= RC_MAX_TEXTURES )
+		return;
+	for( int i = 0; i < rc_decal_next; i++ )
+	{
+		decal_t *d = &rc_decal_pool[i];
+		if( FBitSet( d->flags, FDECAL_PERMANENT ))
+			continue;
+		if( !texture || d->texture == texture )
+			rc_decal_unlink( d );
+	}
+}
+
+static int R_CreateDecalList( struct decallist_s *pList )
+{
+	(void)pList;
+	if( !rc.warned[2] ) { rc.warned[2] = true; gEngfuncs.Con_Reportf( "ref_cuda: R_CreateDecalList (decals in save games) is not built\n" ); }
+	return 0;
+}
+
+/* R_ClearAllDecals (r_decals.c:1024): every pool entry leaves its face */
+static void R_ClearAllDecals( void )
+{
+	for( int i = 0; i < MAX_RENDER_DECALS; i++ )
+		rc_decal_unlink( &rc_decal_pool[i] );
+}
+
+/* R_ClearDecals (r_decals.c:57), at R_NewMap: the pool starts over */
+static void rc_clear_decals( void )
+{
+	memset( rc_decal_pool, 0, sizeof( rc_decal_pool ));
+	rc_decal_next = 0;
+	rc_free( rc_decal_gen ); rc_decal_gen = NULL; rc_decal_gen_n = 0;
+	rc_decals_dirty = true;
+}
+
+/*
+ * The device's view of the lists: per world face the slice of its decals, per decal and mip level the rectangle of the
+ * block it covers and the part of the picture it shows - the integer set-up of R_DrawSurfaceDecals (r_surf.c:914-990),
+ * which depends on the face, the decal and the mip only.
+ */
+static void rc_send_decals( void )
+{
+	if( !rc_decals_dirty || !rc.world )
+		return;
+	rc_decals_dirty = false;
+	const model_t *w = rc.world;
+	const int ns = w->numsurfaces;
+	int32_t *first = rc_malloc( sizeof( int32_t ) * 2 * Q_max( 1, ns ));
+	int total = 0;
+	for( int i = 0; i < ns; i++ )
+		for( const decal_t *d = w->surfaces[i].pdecals; d; d = ( d == d->pnext ) ? NULL : d->pnext )
+			total++;
+	rc_ddecal_t *recs = rc_malloc( sizeof( rc_ddecal_t ) * Q_max( 1, total ));
+	memset( recs, 0, sizeof( rc_ddecal_t ) * Q_max( 1, total ));
+	int n = 0;
+	for( int i = 0; i < ns; i++ )
+	{
+		const msurface_t *fa = &w->surfaces[i];
+		first[2 * i] = n; first[2 * i + 1] = 0;
+		for( const decal_t *p = fa->pdecals; p; p = ( p == p->pnext ) ? NULL : p->pnext )
+		{
+			rc_ddecal_t *o = &recs[n];
+			const int texnum = ( p->texture >= 0 && p->texture < RC_MAX_TEXTURES ) ? p->texture : 0;
+			const rc_image_t *img = &rc.images[texnum];
+			const rc_texture_t *te = rc_texture_entry( texnum );
+			if( !RC_IMAGE_LIVE( img ) || !te )
+				continue; /* !tex->pixels[0] */
+			vec3_t basis[3];
+			const float *tu = fa->texinfo->vecs[0], *tv = fa->texinfo->vecs[1];
+			rc_decal_basis( fa, basis );
+			const int w0 = fabs( img->width * DotProduct( tu, basis[0] )) + fabs( img->height * DotProduct( tu, basis[1] ));
+			const int h0 = fabs( img->width * DotProduct( tv, basis[0] )) + fabs( img->height * DotProduct( tv, basis[1] ));
+			const int x0 = DotProduct( p->position, tu ) + tu[3] - fa->texturemins[0] - w0 / 2;
+			const int y0 = DotProduct( p->position, tv ) + tv[3] - fa->texturemins[1] - h0 / 2;
+			o->tex_ofs = img->has_alpha ? te->alpha_ofs : te->ofs[0];
+			o->texwidth = img->width;
+			o->transparent = img->has_alpha ? 1 : 0;
+			for( int mip = 0; mip < 4; mip++ )
+			{
+				rc_decalmip_t *dm = &o->mip[mip];
+				const int surfwidth = fa->info->lightextents[0] >> mip, surfheight = fa->info->lightextents[1] >> mip;
+				int s1 = 0, t1 = 0, s2 = img->width, t2 = img->height;
+				int x = x0 >> mip, y = y0 >> mip, ww = w0 >> mip, hh = h0 >> mip;
+				if( ww < 1 || hh < 1 )
+					continue;
+				if( x < 0 ) { s1 += ( -x ) * ( s2 - s1 ) / ww; x = 0; }
+				if( x + ww > surfwidth ) { s2 -= ( x + ww - surfwidth ) * ( s2 - s1 ) / ww; ww = surfwidth - x; }
+				if( y + hh > surfheight ) { t2 -= ( y + hh - surfheight ) * ( t2 - t1 ) / hh; hh = surfheight - y; }
+				if( s1 < 0 ) s1 = 0;
+				if( t1 < 0 ) t1 = 0;
+				if( s2 > img->width ) s2 = img->width;
+				if( t2 > img->height ) t2 = img->height;
+				if( s1 >= s2 || t1 >= t2 || !ww )
+					continue;
+				int height = hh, skip = 0;
+				if( y < 0 ) { skip = -y; height += y; y = 0; }
+				if( ww < 0 || height <= 0 || hh == 0 )
+					continue; /* the reference's loops would not run (or would run off the block) */
+				unsigned fstep = ( s2 - s1 ) * 0x10000 / ww;
+				if( ww == s2 - s1 )
+					fstep = 0x10000;
+				dm->valid = 1; dm->x = x; dm->y = y; dm->w = ww; dm->h = hh; dm->height = height; dm->skip = skip;
+				dm->s1 = s1; dm->t1 = t1; dm->tspan = t2 - t1; dm->fstep = fstep;
+			}
+			n++; first[2 * i + 1]++;
+		}
+	}
+	rc_decal_gen_ensure();
+	RC_CHECK_DEV( rc_dev_set_decals( recs, n, first, rc_decal_gen, ns ));
+	rc_free( recs ); rc_free( first );
+}
+
 static qboolean R_StudioFillAPI( struct engine_studio_api_s *api, struct r_studio_interface_s *pDefaultDraw ) { (void)api; (void)pDefaultDraw; return false; }
 static void R_StudioSetDrawInterface( struct r_studio_interface_s *pDraw ) { (void)pDraw; }
 static void R_SetSkyCloudsTextures( int solidskyTexture, int alphaskyTexture ) { (void)solidskyTexture; (void)alphaskyTexture; }
@@ -2733,6 +3231,7 @@ static void CL_DrawTracers( double frametime, particle_t *tracers )
 		const color24 color = rc_tracer_colors[p->color];
 		rc_tri_color4f( 1.0f * alpha / 255 / 255 * color.r, 1.0f * alpha / 255 / 255 * color.g, 1.0f * alpha / 255 / 255 * color.b, 1.0f );
 		rc_item_t *it = rc_new_item( RC_ITEM_TRACER );
+		rc.ntracers++;
 		it->count = 2;
 		it->light = (int32_t)( rc.tri.light << 8 );
 		it->scale = rc_tracer_size[p->type];

@@ -208,6 +208,27 @@ typedef struct
 	int32_t glow;                 /* RC_ITEM_SPRITE drawn with kRenderGlow: its column in the batch's per-view glow records; else -1 */
 } rc_item_t; /* 164 B */
 
+/* a decal of a face, as R_DrawSurfaceDecals (ref/soft/r_surf.c:914) blits it into a cache block of the face: per mip level
+ * the rectangle of the block it covers and the part of the picture that lands there (the reference's integer set-up,
+ * done on the host: it depends on the face, the decal and the mip only) */
+typedef struct
+{
+	int32_t  valid;
+	int32_t  x, y, w;        /* first column / row and width of the rectangle in the block */
+	int32_t  h;              /* the row divisor: sv = ( skip + v ) * tspan / h + t1 */
+	int32_t  height, skip;   /* rows drawn, rows of the rectangle above the block */
+	int32_t  s1, t1, tspan;  /* first picture column, first picture row, t2 - t1 */
+	uint32_t fstep;          /* 16.16 picture columns per block column */
+} rc_decalmip_t;
+
+typedef struct
+{
+	int32_t tex_ofs;         /* texel arena offset of the picture (its alpha plane when it has one) */
+	int32_t texwidth;
+	int32_t transparent;     /* the picture has an alpha plane: 3-bit alpha in the top bits of a texel */
+	rc_decalmip_t mip[4];
+} rc_ddecal_t;
+
 /* a kRenderGlow sprite for one view (R_SpriteOccluded / R_SpriteGlowBlend, ref/soft/r_sprite.c:59-117): whether it is drawn
  * (scissor, the engine's occlusion trace from this eye, fade) and the size and colour its distance from this eye gives it.
  * Computed on the host per (view, sprite) - the trace is an engine callback - and laid out [view][sprite]. */

@@ -500,6 +500,42 @@ RC_HD void rc_tri_shade( const rc_blendluts_t *L, int drawer, uint32_t color, ui
 }
 
 /* ------------------------------------------------------------------------------------------ */
+/* R_DrawSurfaceDecals (ref/soft/r_surf.c:990-1044) for one texel (tx, ty) of a cache block at `mip`: the face's decals in
+ * list order over *px.  Returns 1 when a decal wrote the texel. */
+RC_HD int rc_decal_texel( const rc_blendluts_t *L, const uint16_t *texels, const rc_ddecal_t *dl, int32_t ndecals, int32_t mip,
+	int32_t tx, int32_t ty, uint32_t *px )
+{
+	int touched = 0;
+	for( int32_t k = 0; k < ndecals; k++ )
+	{
+		const rc_decalmip_t *dm = &dl[k].mip[mip];
+		const int32_t u = tx - dm->x, v = ty - dm->y;
+		if( !dm->valid || u < 0 || u >= dm->w || v < 0 || v >= dm->height )
+			continue;
+		const int32_t sv = ( dm->skip + v ) * dm->tspan / dm->h + dm->t1;
+		const uint32_t f = (uint32_t)u * dm->fstep;
+		uint32_t src = texels[dl[k].tex_ofs + sv * dl[k].texwidth + dm->s1 + (int32_t)( f >> 16 )];
+		uint32_t alpha = 7;
+		if( dl[k].transparent )
+		{
+			alpha &= src >> 13;
+			src = ( src << 3 ) & 0xFFFFu;
+		}
+		if( alpha == 0 )
+			continue;
+		if( alpha < 7 )
+		{
+			if( *px == 0x0349u ) /* TRANSPARENT_COLOR */
+				continue;
+			*px = rc_blend_alpha( L, alpha, src, *px );
+		}
+		else *px = src;
+		touched = 1;
+	}
+	return touched;
+}
+
+/* ------------------------------------------------------------------------------------------ */
 /* translucent brush entities: one pixel of D_AlphaSpans16 / D_BlendSpans16 / D_AddSpans16 / D_DrawTurbulent8ZSpan
  * (ref/soft/r_scan.c:698,898,1109,59): texel = what the span's s, t select in the cache block (the texture, for water),
  * izi the span's 1/z accumulator at the pixel */

@@ -132,6 +132,12 @@ class Renderer:
         pp = (C.c_float * 3)(*[float(x) for x in pos])
         L.xh_decal_shoot(int(texture), pp, int(flags), float(scale))
 
+    def remove_decals(self, texture=0):
+        L = self.host.lib
+        L.xh_remove_decals.argtypes = [C.c_int]
+        L.xh_remove_decals.restype = None
+        L.xh_remove_decals(int(texture))
+
     def clear_decals(self):
         L = self.host.lib
         L.xh_clear_decals.restype = None
@@ -499,7 +505,7 @@ def sprite_image(seed, w=64, h=64):
 def add_sprites(r, cams, count=32, ahead=96.0):
     """BASELINE config C5's sprites: `count` translucent sprites (additive, alpha-tested texture and colour-blended, all
     parallel-oriented) `ahead` units in front of the first `count` cameras; sorted per view by the renderer."""
-    TF_HAS_ALPHA = 1 << 20
+    TF_HAS_ALPHA = 1 << 16
     mods = [r.create_sprite("spr_c5_add", sprite_image(11), sprtype=2, texformat=1),
             r.create_sprite("spr_c5_alpha", sprite_image(12), sprtype=2, texformat=3, texflags=TF_HAS_ALPHA),
             r.create_sprite("spr_c5_blend", sprite_image(13, 32, 48), sprtype=2, texformat=0)]
@@ -520,16 +526,20 @@ def compare_frames(a_col, a_z, b_col, b_z):
     return same_c, same_z
 
 
-def shoot_decals(r, cams, z, seed=5):
-    """R_DecalShoot at the point the middle pixel of every view in cams looks at (z: that renderer's 1/z frames of cams):
-    a 32x32 decal picture with an alpha channel, on the world model.  Returns the points."""
+def shoot_decals(r, cams, z, seed=5, scale=1.0, opaque=False):
+    """R_DecalShoot at the point the middle pixel of every view in cams looks at (z: 1/z frames of cams): a decal picture with
+    an alpha channel (or an opaque one), on the world model.  Returns the points."""
     rng = np.random.default_rng(seed)
-    img = np.zeros((32, 32, 4), np.uint8)
+    TF_HAS_ALPHA = 1 << 16
+    size = 32 if not opaque else 16
+    img = np.zeros((size, size, 4), np.uint8)
     img[..., 0] = 255
-    img[..., 1] = rng.integers(0, 255, (32, 32))
-    img[..., 3] = rng.integers(0, 255, (32, 32))
-    img[8:24, 8:24, 3] = 255
-    tex = r.load_pic("{decal1", img, 0)
+    img[..., 1] = rng.integers(0, 255, (size, size))
+    img[..., 2] = 40 * opaque
+    img[..., 3] = 255 if opaque else rng.integers(0, 255, (size, size))
+    if not opaque:
+        img[8:24, 8:24, 3] = 255
+    tex = r.load_pic("{decal%d" % seed, img, 0 if opaque else TF_HAS_ALPHA)
     pts = []
     cams = np.asarray(cams, dtype=np.float32).reshape(-1, 6)
     h, w = z.shape[1:3]
@@ -538,6 +548,6 @@ def shoot_decals(r, cams, z, seed=5):
         p, y = np.radians(c[3]), np.radians(c[4])
         fwd = np.array([np.cos(p) * np.cos(y), np.cos(p) * np.sin(y), -np.sin(p)])
         pt = c[:3] + fwd * depth
-        r.decal_shoot(tex, pt, 0, 1.0)
+        r.decal_shoot(tex, pt, 0, scale)
         pts.append(pt)
     return pts
