@@ -1026,6 +1026,16 @@ int ensure_batch( int nviews, int width, int height )
 				}
 			}
 		}
+		if( const char *e = getenv( "RC_VIS_STAGE" )) /* measurement only: which of tree / scratch / lists k_viswalk keeps in shared memory */
+		{
+			const int want = atoi( e );
+			size_t n2 = ((((size_t)( w.visbytes_padded >> 2 ) + w.nodewords + w.leafwords + w.surfwords ) * 4 ) + 15 ) & ~(size_t)15;
+			int got = 0;
+			if(( want & VW_STAGE_TREE ) && ( w.vis_stage & VW_STAGE_TREE )) { got |= VW_STAGE_TREE; n2 += rc_vis_tree_bytes( &sc ); }
+			if(( want & VW_STAGE_SCRATCH ) && ( w.vis_stage & VW_STAGE_SCRATCH )) { got |= VW_STAGE_SCRATCH; n2 += (size_t)w.stack_ints * 4; }
+			if(( want & VW_STAGE_LISTS ) && ( w.vis_stage & VW_STAGE_LISTS )) { got |= VW_STAGE_LISTS; n2 += (( 2 * ( (size_t)sc.numsurfaces + sc.nummarks )) + 15 ) & ~(size_t)15; }
+			w.vis_stage = got; need = n2;
+		}
 		w.vis_smem = (int32_t)need;
 	}
 	{
@@ -1033,6 +1043,19 @@ int ensure_batch( int nviews, int width, int height )
 		int per_sm = 0;
 		CK( cudaOccupancyMaxActiveBlocksPerMultiprocessor( &per_sm, k_viswalk<VW_NTHREADS>, VW_NTHREADS, (size_t)w.vis_smem ));
 		if( per_sm < 1 ) per_sm = 1;
+		/* a batch with many more views than resident blocks gains more from blocks than from a staged tree: keep only the
+		 * walk's scratch in shared memory (measured, 4096 views of Map S: 0.96 -> 0.60 ms; 256 views: staged is faster,
+		 * 49 vs 57 us - profiles/r03t_viswalk_staging.txt) */
+		if( !getenv( "RC_VIS_STAGE" ) && ( w.vis_stage & VW_STAGE_SCRATCH ) && ( w.vis_stage & VW_STAGE_TREE ) && nviews >= 8 * per_sm * D.num_sms )
+		{
+			const size_t light = (((((size_t)( w.visbytes_padded >> 2 ) + w.nodewords + w.leafwords + w.surfwords ) * 4 ) + 15 ) & ~(size_t)15 ) + (size_t)w.stack_ints * 4;
+			int per_sm2 = 0;
+			CK( cudaOccupancyMaxActiveBlocksPerMultiprocessor( &per_sm2, k_viswalk<VW_NTHREADS>, VW_NTHREADS, light ));
+			if( per_sm2 > per_sm )
+			{
+				w.vis_stage = VW_STAGE_SCRATCH; w.vis_smem = (int32_t)light; per_sm = per_sm2;
+			}
+		}
 		D.vw_grid = per_sm * D.num_sms;
 	}
 
