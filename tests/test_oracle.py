@@ -364,3 +364,29 @@ def test_scalar_decals_match_oracle(pkg, scene):
     a, z = emu.render_views(cams)
     rc, rz = so.render_views(cams)
     assert np.array_equal(a, rc) and np.array_equal(z, rz), (a == rc).mean()
+
+
+def test_scalar_attachment_followers_match_oracle(pkg, scene):
+    """R_StudioCalcAttachments (ref/soft/r_studio.c:1212) + the MOVETYPE_FOLLOW branch of R_DrawSpriteModel (r_sprite.c:170): sprites
+    that ride on the attachment points of animated studio models are drawn where the model's bones put them this frame"""
+    from importlib import import_module
+    mdlgen = import_module("xash3d-fwgs_b200.tools.mdlgen")
+    m = scene.make_map("small", ncameras=64)
+    emu = scene.Renderer(EMU_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    mdl = mdlgen.generate(nbones=12, attachments=[(11, (6.0, 0.0, 4.0)), (5, (0.0, 9.0, 0.0)), (2, (-7.0, 3.0, 1.0))])
+    res = []
+    for r in (emu, so):
+        r.set_time(1.0)
+        scene.add_studio_models(r, m.cameras, 6, nbones=12, mdl=mdl)
+        spr = r.create_sprite("spr_follow", scene.sprite_image(17, 32, 32), sprtype=2, texformat=1)
+        for k in range(6):
+            # entity k + 1 is the k-th model; body = attachment number + 1 (0: the parent's origin)
+            r.add_entity(spr, (0, 0, 0), rendermode=5, renderamt=255, rendercolor=(255, 255, 255), movetype=12, aiment=k + 1, body=k % 4, scale=0.5)
+        res.append(r.render_views(m.cameras[:6]))
+    bare = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    bare.set_time(1.0)
+    scene.add_studio_models(bare, m.cameras, 6, nbones=12, mdl=mdl)
+    nb, _ = bare.render_views(m.cameras[:6])
+    assert (res[1][0] != nb).mean() > 0.001, "the oracle drew no follower"
+    assert np.array_equal(res[0][0], res[1][0]) and np.array_equal(res[0][1], res[1][1]), (res[0][0] == res[1][0]).mean()

@@ -1862,6 +1862,13 @@ static void rc_add_studio( cl_entity_t *e )
 	matrix3x4 rotation;
 	if( !rc_studio_skeleton( e, hdr, rotation, bones, light ))
 		return;
+	/* R_StudioCalcAttachments (r_studio.c:1212): where the model's attachment points are this frame - sprites and models
+	 * that follow the entity (MOVETYPE_FOLLOW, body = attachment) are placed there */
+	{
+		const mstudioattachment_t *att = (const mstudioattachment_t *)((const byte *)hdr + hdr->attachmentindex );
+		for( int i = 0; i < Q_min( MAXSTUDIOATTACHMENTS, hdr->numattachments ); i++ )
+			Matrix3x4_VectorTransform( light[att[i].bone], att[i].org, e->attachment[i] );
+	}
 	/* attachments of a model that has none: the entity origin (R_StudioClientEvents, r_studio.c:2172) */
 	if( hdr->numattachments <= 0 && gp_cl->time != gp_cl->oldtime )
 		for( int i = 0; i < 4; i++ ) Matrix3x4_OriginFromMatrix( rotation, e->attachment[i] );

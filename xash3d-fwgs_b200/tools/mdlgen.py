@@ -24,7 +24,8 @@ def _name(s: str, n: int) -> bytes:
 
 
 def generate(nbones: int = 32, ring: int = 48, seglen: float = 4.0, radius: float = 9.0, nframes: int = 30, skin: int = 128,
-             seed: int = 0xB200, texflags: int = 0, name: str = "synth.mdl") -> bytes:
+             seed: int = 0xB200, texflags: int = 0, name: str = "synth.mdl", attachments=()) -> bytes:
+    """attachments: (bone, (x, y, z)) pairs - mstudioattachment_t records (R_StudioCalcAttachments)"""
     rng = np.random.default_rng(seed)
     # ---- skin: 8-bit indices + palette
     ys, xs = np.mgrid[0:skin, 0:skin]
@@ -167,6 +168,11 @@ def generate(nbones: int = 32, ring: int = 48, seglen: float = 4.0, radius: floa
     align()
     blob[textureindex : textureindex + 80] = _name("skin.bmp", 64) + struct.pack("<Iiii", texflags, skin, skin, texturedataindex)
 
+    attachindex = len(blob)
+    for k, (abone, aorg) in enumerate(attachments):
+        blob += _name("attach%d" % k, 32) + struct.pack("<2i", 0, int(abone)) + struct.pack("<3f", *[float(v) for v in aorg]) + struct.pack("<9f", *([0.0] * 9))
+    align()
+
     hdr = struct.pack("<ii", (ord("T") << 24) | (ord("S") << 16) | (ord("D") << 8) | ord("I"), 10) + _name(name, 64) + struct.pack("<i", len(blob))
     hdr += struct.pack("<3f", 0, 0, 0)  # eyeposition
     hdr += struct.pack("<6f", 0, 0, 0, 0, 0, 0)  # min, max
@@ -180,7 +186,7 @@ def generate(nbones: int = 32, ring: int = 48, seglen: float = 4.0, radius: floa
     hdr += struct.pack("<3i", 1, textureindex, texturedataindex)
     hdr += struct.pack("<3i", 1, 1, skinindex)
     hdr += struct.pack("<2i", 1, bodypartindex)
-    hdr += struct.pack("<2i", 0, boneindex)  # attachments: none
+    hdr += struct.pack("<2i", len(attachments), attachindex if attachments else boneindex)
     hdr += struct.pack("<4i", 0, 0, 0, 0)  # studiohdr2index, unused x3
     hdr += struct.pack("<2i", 0, 0)  # transitions
     assert len(hdr) == 244, len(hdr)
