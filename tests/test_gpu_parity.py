@@ -767,3 +767,28 @@ def test_decals_match_oracle(pkg, scene):
     rc, rz = so.render_views(cams)
     cc, cz = cu.render_views(cams)
     assert np.array_equal(cc, rc) and np.array_equal(cz, rz), ((cc == rc).mean(), (cz == rz).mean())
+
+
+@pytest.mark.gpu
+def test_attachments_and_followers_match_oracle(pkg, scene):
+    """studio attachments with sprites riding on them, and models that follow models (MOVETYPE_FOLLOW, R_StudioMergeBones), on the
+    device: 12 animated models with attachment points, a sprite and a rider each, 16 views"""
+    from importlib import import_module
+    mdlgen = import_module("xash3d-fwgs_b200.tools.mdlgen")
+    m = scene.make_map("small", ncameras=64)
+    cu = scene.Renderer(pkg.REF_CUDA_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    parent = mdlgen.generate(nbones=12, attachments=[(11, (6.0, 0.0, 4.0)), (5, (0.0, 9.0, 0.0)), (2, (-7.0, 3.0, 1.0))])
+    rider = mdlgen.generate(nbones=6, ring=16, radius=14.0, seed=77, name="rider.mdl", bone_names=["bone08", "bone09", "w0", "w1", "w2", "w3"])
+    res = []
+    for r in (cu, so):
+        r.set_time(1.0)
+        scene.add_studio_models(r, m.cameras, 12, nbones=12, mdl=parent)
+        spr = r.create_sprite("spr_follow", scene.sprite_image(17, 32, 32), sprtype=2, texformat=1)
+        mi = r.load_studio("models/rider.mdl", rider)
+        for k in range(12):
+            r.add_entity(spr, (0, 0, 0), rendermode=5, renderamt=255, rendercolor=(255, 255, 255), movetype=12, aiment=k + 1, body=k % 4, scale=0.5)
+        for k in range(12):
+            r.add_entity(mi, (0, 0, 0), angles=(0.0, 11.0 * k, 0.0), frame=(5 * k) % 30, movetype=12, aiment=k + 1, animtime=0.4)
+        res.append(r.render_views(m.cameras[:16]))
+    assert np.array_equal(res[0][0], res[1][0]) and np.array_equal(res[0][1], res[1][1]), ((res[0][0] == res[1][0]).mean(), (res[0][1] == res[1][1]).mean())

@@ -390,3 +390,29 @@ def test_scalar_attachment_followers_match_oracle(pkg, scene):
     nb, _ = bare.render_views(m.cameras[:6])
     assert (res[1][0] != nb).mean() > 0.001, "the oracle drew no follower"
     assert np.array_equal(res[0][0], res[1][0]) and np.array_equal(res[0][1], res[1][1]), (res[0][0] == res[1][0]).mean()
+
+
+def test_scalar_follower_models_match_oracle(pkg, scene):
+    """models that ride on other models (MOVETYPE_FOLLOW, R_DrawStudioModel's branch r_studio.c:2869 + R_StudioMergeBones :780): the
+    follower's bones that carry a parent bone's name take the parent's matrices, the others hang off them with its own animation"""
+    from importlib import import_module
+    mdlgen = import_module("xash3d-fwgs_b200.tools.mdlgen")
+    m = scene.make_map("small", ncameras=64)
+    emu = scene.Renderer(EMU_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    parent = mdlgen.generate(nbones=12)
+    rider = mdlgen.generate(nbones=6, ring=16, radius=14.0, seed=77, name="rider.mdl", bone_names=["bone08", "bone09", "w0", "w1", "w2", "w3"])
+    res = []
+    for r in (emu, so):
+        r.set_time(1.0)
+        scene.add_studio_models(r, m.cameras, 6, nbones=12, mdl=parent)
+        mi = r.load_studio("models/rider.mdl", rider)
+        for k in range(6):
+            r.add_entity(mi, (0, 0, 0), angles=(0.0, 11.0 * k, 0.0), frame=(5 * k) % 30, movetype=12, aiment=k + 1, animtime=0.4)
+        res.append(r.render_views(m.cameras[:6]))
+    bare = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    bare.set_time(1.0)
+    scene.add_studio_models(bare, m.cameras, 6, nbones=12, mdl=parent)
+    nb, _ = bare.render_views(m.cameras[:6])
+    assert (res[1][0] != nb).mean() > 0.002, "the oracle drew no follower"
+    assert np.array_equal(res[0][0], res[1][0]) and np.array_equal(res[0][1], res[1][1]), (res[0][0] == res[1][0]).mean()

@@ -1584,11 +1584,9 @@ static void rc_studio_rotations( const cl_entity_t *e, studiohdr_t *hdr, float p
 	if( pseqdesc->motiontype & STUDIO_Z ) pos[pseqdesc->motionbone][2] = 0.0f;
 }
 
-/* R_StudioSetUpTransform + R_StudioSetupBones (r_studio.c:523,840): bone and light matrices of the entity */
-static qboolean rc_studio_skeleton( cl_entity_t *e, studiohdr_t *hdr, matrix3x4 rotation, matrix3x4 *bones, matrix3x4 *light )
+/* R_StudioSetUpTransform (r_studio.c:523): the entity's placement */
+static void rc_studio_transform( cl_entity_t *e, matrix3x4 rotation )
 {
-	static vec3_t pos[MAXSTUDIOBONES], pos2[MAXSTUDIOBONES], pos3[MAXSTUDIOBONES], pos4[MAXSTUDIOBONES], pos1b[MAXSTUDIOBONES];
-	static vec4_t q[MAXSTUDIOBONES], q2[MAXSTUDIOBONES], q3[MAXSTUDIOBONES], q4[MAXSTUDIOBONES], q1b[MAXSTUDIOBONES];
 	vec3_t origin, angles;
 	VectorCopy( e->origin, origin ); VectorCopy( e->angles, angles );
 	if( e->curstate.movetype == MOVETYPE_STEP && !FBitSet( gp_host->features, ENGINE_COMPUTE_STUDIO_LERP ))
@@ -1596,13 +1594,32 @@ static qboolean rc_studio_skeleton( cl_entity_t *e, studiohdr_t *hdr, matrix3x4 
 	if( !FBitSet( gp_host->features, ENGINE_COMPENSATE_QUAKE_BUG ))
 		angles[PITCH] = -angles[PITCH];
 	Matrix3x4_CreateFromEntity( rotation, angles, origin, 1.0f );
+}
+
+/* R_StudioFxTransform (r_studio.c:617) as far as it is built: kRenderFxExplode stretches the root bones */
+static void rc_studio_fx_transform( const cl_entity_t *e, matrix3x4 bone )
+{
+	if( e->curstate.renderfx == kRenderFxExplode )
+	{
+		float scale = 1.0f + ( gp_cl->time - e->curstate.animtime ) * 10.0f;
+		if( scale > 2.0f ) scale = 2.0f;
+		bone[0][1] *= scale; bone[1][1] *= scale; bone[2][1] *= scale;
+	}
+}
+
+/* R_StudioSetUpTransform + R_StudioSetupBones (r_studio.c:523,840): bone and light matrices of the entity */
+static qboolean rc_studio_skeleton( cl_entity_t *e, model_t *mod, studiohdr_t *hdr, matrix3x4 rotation, matrix3x4 *bones, matrix3x4 *light )
+{
+	static vec3_t pos[MAXSTUDIOBONES], pos2[MAXSTUDIOBONES], pos3[MAXSTUDIOBONES], pos4[MAXSTUDIOBONES], pos1b[MAXSTUDIOBONES];
+	static vec4_t q[MAXSTUDIOBONES], q2[MAXSTUDIOBONES], q3[MAXSTUDIOBONES], q4[MAXSTUDIOBONES], q1b[MAXSTUDIOBONES];
+	rc_studio_transform( e, rotation );
 
 	if( e->curstate.sequence >= hdr->numseq ) e->curstate.sequence = 0;
 	const int nb = hdr->numbones;
 	const double time = gp_cl->time;
 	mstudioseqdesc_t *pseqdesc = (mstudioseqdesc_t *)((byte *)hdr + hdr->seqindex ) + e->curstate.sequence;
 	const float f = rc_studio_frame( e, pseqdesc, time );
-	mstudioanim_t *panim = gEngfuncs.R_StudioGetAnim( hdr, e->model, pseqdesc );
+	mstudioanim_t *panim = gEngfuncs.R_StudioGetAnim( hdr, mod, pseqdesc );
 	if( !panim )
 		return false;
 	rc_studio_rotations( e, hdr, pos, q, pseqdesc, panim, f );
@@ -1627,7 +1644,7 @@ static qboolean rc_studio_skeleton( cl_entity_t *e, studiohdr_t *hdr, matrix3x4 
 	{
 		/* blend from the previous sequence */
 		pseqdesc = (mstudioseqdesc_t *)((byte *)hdr + hdr->seqindex ) + e->latched.prevsequence;
-		panim = gEngfuncs.R_StudioGetAnim( hdr, e->model, pseqdesc );
+		panim = gEngfuncs.R_StudioGetAnim( hdr, mod, pseqdesc );
 		if( !panim ) return false;
 		rc_studio_rotations( e, hdr, pos1b, q1b, pseqdesc, panim, e->latched.prevframe );
 		if( pseqdesc->numblends > 1 )
@@ -1659,17 +1676,81 @@ static qboolean rc_studio_skeleton( cl_entity_t *e, studiohdr_t *hdr, matrix3x4 
 		{
 			Matrix3x4_ConcatTransforms( bones[i], rotation, bonematrix );
 			Matrix3x4_Copy( light[i], bones[i] );
-			if( e->curstate.renderfx == kRenderFxExplode )
-			{
-				float scale = 1.0f + ( time - e->curstate.animtime ) * 10.0f;
-				if( scale > 2.0f ) scale = 2.0f;
-				bones[i][0][1] *= scale; bones[i][1][1] *= scale; bones[i][2][1] *= scale;
-			}
+			rc_studio_fx_transform( e, bones[i] );
 		}
 		else
 		{
 			Matrix3x4_ConcatTransforms( bones[i], bones[pbones[i].parent], bonematrix );
 			Matrix3x4_ConcatTransforms( light[i], light[pbones[i].parent], bonematrix );
+		}
+	}
+	return true;
+}
+
+/*
+ * A model that rides on another one (MOVETYPE_FOLLOW: a carried weapon, a rider) - R_DrawStudioModel's branch
+ * (r_studio.c:2869) + R_StudioMergeBones (:780): a skeleton is set up for the parent entity and cached, the follower takes
+ * the parent's place, and every bone of it that carries the name of a cached bone takes that bone's matrices; the others
+ * hang off them with the follower's own animation.
+ */
+static qboolean rc_studio_follow_skeleton( cl_entity_t *e, studiohdr_t *hdr, matrix3x4 rotation, matrix3x4 *bones, matrix3x4 *light )
+{
+	static matrix3x4 pbone[MAXSTUDIOBONES], plight[MAXSTUDIOBONES];
+	static vec3_t pos[MAXSTUDIOBONES];
+	static vec4_t q[MAXSTUDIOBONES];
+	cl_entity_t *parent = ( rc.entities && e->curstate.aiment > 0 && (uint)e->curstate.aiment < rc.max_entities ) ? &rc.entities[e->curstate.aiment] : NULL;
+	if( !parent || !parent->model || parent->model->type != mod_studio )
+		return false;
+	/* R_FindParentEntity: the parent has to be in this frame's lists */
+	cl_entity_t *found = NULL;
+	for( int i = 0; i < rc.num_solid && !found; i++ ) if( rc.solid_ents[i]->index == e->curstate.aiment ) found = rc.solid_ents[i];
+	for( int i = 0; i < rc.num_trans && !found; i++ ) if( rc.trans_ents[i]->index == e->curstate.aiment ) found = rc.trans_ents[i];
+	if( !found || found->player || found->curstate.movetype == MOVETYPE_FOLLOW || found->curstate.renderfx == kRenderFxDeadPlayer )
+		return false; /* (players and chains of followers are not built) */
+	/* the parent's pass runs with RI.currentmodel still the follower's (R_DrawEntitiesOnList set it, r_main.c:548, and
+	 * R_DrawStudioModel changes RI.currententity only): the skeleton that is cached and merged from is the FOLLOWER's
+	 * model posed by the parent's entity state - origin, angles, sequence, frame, controllers */
+	studiohdr_t *phdr = hdr;
+	matrix3x4 prot;
+	if( !rc_studio_skeleton( found, e->model, phdr, prot, pbone, plight ))
+		return false;
+	VectorCopy( found->curstate.origin, e->curstate.origin );
+	VectorCopy( found->origin, e->origin );
+
+	rc_studio_transform( e, rotation );
+	if( e->curstate.sequence >= hdr->numseq ) e->curstate.sequence = 0;
+	mstudioseqdesc_t *pseqdesc = (mstudioseqdesc_t *)((byte *)hdr + hdr->seqindex ) + e->curstate.sequence;
+	const float f = rc_studio_frame( e, pseqdesc, gp_cl->time );
+	mstudioanim_t *panim = gEngfuncs.R_StudioGetAnim( hdr, e->model, pseqdesc );
+	if( !panim )
+		return false;
+	rc_studio_rotations( e, hdr, pos, q, pseqdesc, panim, f );
+	const mstudiobone_t *mybones = (const mstudiobone_t *)((const byte *)hdr + hdr->boneindex );
+	const mstudiobone_t *parbones = (const mstudiobone_t *)((const byte *)phdr + phdr->boneindex );
+	for( int i = 0; i < hdr->numbones; i++ )
+	{
+		int j;
+		for( j = 0; j < phdr->numbones; j++ )
+			if( !strcasecmp( mybones[i].name, parbones[j].name ))
+			{
+				Matrix3x4_Copy( bones[i], pbone[j] );
+				Matrix3x4_Copy( light[i], plight[j] );
+				break;
+			}
+		if( j < phdr->numbones )
+			continue;
+		matrix3x4 bonematrix;
+		Matrix3x4_FromOriginQuat( bonematrix, q[i], pos[i] );
+		if( mybones[i].parent == -1 )
+		{
+			Matrix3x4_ConcatTransforms( bones[i], rotation, bonematrix );
+			Matrix3x4_Copy( light[i], bones[i] );
+			rc_studio_fx_transform( e, bones[i] );
+		}
+		else
+		{
+			Matrix3x4_ConcatTransforms( bones[i], bones[mybones[i].parent], bonematrix );
+			Matrix3x4_ConcatTransforms( light[i], light[mybones[i].parent], bonematrix );
 		}
 	}
 	return true;
@@ -1850,18 +1931,28 @@ static void rc_add_studio( cl_entity_t *e )
 	studiohdr_t *hdr = (studiohdr_t *)gEngfuncs.Mod_Extradata( mod_studio, e->model );
 	if( !hdr )
 		return;
-	if( e->player || e->curstate.movetype == MOVETYPE_FOLLOW || e->curstate.renderfx == kRenderFxGlowShell || e->curstate.renderfx == kRenderFxDeadPlayer
+	if( e->player || e->curstate.renderfx == kRenderFxGlowShell || e->curstate.renderfx == kRenderFxDeadPlayer
 		|| FBitSet( hdr->flags, STUDIO_HAS_BONEWEIGHTS ) || hdr->numbones > MAXSTUDIOBONES )
 	{
-		if( !rc.warned[5] ) { rc.warned[5] = true; gEngfuncs.Con_Reportf( "ref_cuda: player models, attached (MOVETYPE_FOLLOW) models, glow shells and bone-weighted models are not drawn yet\n" ); }
+		if( !rc.warned[5] ) { rc.warned[5] = true; gEngfuncs.Con_Reportf( "ref_cuda: player models, glow shells and bone-weighted models are not drawn yet\n" ); }
 		return;
 	}
-	if( hdr->numbodyparts == 0 )
-		return;
 	static matrix3x4 bones[MAXSTUDIOBONES], light[MAXSTUDIOBONES];
 	matrix3x4 rotation;
-	if( !rc_studio_skeleton( e, hdr, rotation, bones, light ))
-		return;
+	if( e->curstate.movetype == MOVETYPE_FOLLOW )
+	{
+		if( !rc_studio_follow_skeleton( e, hdr, rotation, bones, light ))
+			return;
+		if( hdr->numbodyparts == 0 )
+			return;
+	}
+	else
+	{
+		if( hdr->numbodyparts == 0 )
+			return;
+		if( !rc_studio_skeleton( e, e->model, hdr, rotation, bones, light ))
+			return;
+	}
 	/* R_StudioCalcAttachments (r_studio.c:1212): where the model's attachment points are this frame - sprites and models
 	 * that follow the entity (MOVETYPE_FOLLOW, body = attachment) are placed there */
 	{

@@ -24,8 +24,9 @@ def _name(s: str, n: int) -> bytes:
 
 
 def generate(nbones: int = 32, ring: int = 48, seglen: float = 4.0, radius: float = 9.0, nframes: int = 30, skin: int = 128,
-             seed: int = 0xB200, texflags: int = 0, name: str = "synth.mdl", attachments=()) -> bytes:
-    """attachments: (bone, (x, y, z)) pairs - mstudioattachment_t records (R_StudioCalcAttachments)"""
+             seed: int = 0xB200, texflags: int = 0, name: str = "synth.mdl", attachments=(), bone_names=None) -> bytes:
+    """attachments: (bone, (x, y, z)) pairs - mstudioattachment_t records (R_StudioCalcAttachments);
+    bone_names: names of the first bones instead of bone00, bone01, ... (R_StudioMergeBones matches bones by name)"""
     rng = np.random.default_rng(seed)
     # ---- skin: 8-bit indices + palette
     ys, xs = np.mgrid[0:skin, 0:skin]
@@ -39,7 +40,7 @@ def generate(nbones: int = 32, ring: int = 48, seglen: float = 4.0, radius: floa
     for i in range(nbones):
         value = (0.0, 0.0, 0.0 if i == 0 else seglen, 0.0, 0.0, 0.0)
         scale = (0.0, 0.0, 0.0, 1.0 / 2048.0, 1.0 / 2048.0, 0.0)  # rotation about x and y is animated
-        bones.append((f"bone{i:02d}", i - 1, value, scale))
+        bones.append((bone_names[i] if bone_names and i < len(bone_names) else f"bone{i:02d}", i - 1, value, scale))
 
     # ---- geometry: vertex ring j of joint i lives in bone i's space
     verts, vbone = [], []
