@@ -1296,8 +1296,8 @@ int launch_slice( const rc_work_t &ws, int k, cudaStream_t st, cudaEvent_t *evs,
 			{
 				k_tri_keys_init<<<D.num_sms * 8, 256, 0, st>>>( ws ); D.launches++;
 				/* x = slot in the pair list (the live ones first; the rest of the upper bound exits at once), y = 128 triangles */
-				dim3 gf( ws.nviews * D.nfast_items, ( D.fast_maxcount + 127 ) / 128 );
-				k_tris_fast<<<gf, 128, 0, st>>>( ws ); D.launches++;
+				dim3 gf( ws.nviews * D.nfast_items, ( D.fast_maxcount + TF_THREADS * TF_ROUNDS - 1 ) / ( TF_THREADS * TF_ROUNDS ));
+				k_tris_fast<<<gf, TF_THREADS, 0, st>>>( ws ); D.launches++;
 				KCHECK( "k_tris_fast", st );
 				k_tris_fast_big<<<D.num_sms * 8, 128, 0, st>>>( ws ); D.launches++;
 				k_tri_resolve<<<D.num_sms * 16, 128, 0, st>>>( sc, ws ); D.launches++;
