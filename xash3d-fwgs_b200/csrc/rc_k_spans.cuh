@@ -51,7 +51,7 @@ static inline size_t rc_events_smem( int32_t ecap, int32_t bitwords )
 	return sizeof( rc_edge_t ) * (size_t)ecap + sizeof( unsigned long long ) * (size_t)ecap + sizeof( uint32_t ) * 2 * ( (size_t)bitwords + 1 );
 }
 
-__global__ void __launch_bounds__( EV_THREADS ) k_events( rc_work_t w )
+__global__ void __launch_bounds__( EV_THREADS, 4 ) k_events( rc_work_t w )
 {
 	extern __shared__ __align__( 16 ) unsigned char ev_smem[];
 	__shared__ int32_t s_wcnt[EV_WARPS][SP_LINES];

@@ -363,7 +363,7 @@ __device__ __forceinline__ int32_t rc_block_excl_scan( int32_t v, int32_t *wsum,
 	return wbase + incl - v;
 }
 
-__global__ void __launch_bounds__( TR_THREADS ) k_tris_ordered( rc_scene_t sc, rc_work_t w, int32_t ntris )
+__global__ void __launch_bounds__( TR_THREADS, 8 ) k_tris_ordered( rc_scene_t sc, rc_work_t w, int32_t ntris )
 {
 	/* a translucent brush entity's scanline spans and a batch of triangle set-ups are never live together */
 	union tr_shared_t
