@@ -359,6 +359,25 @@ void xh_decal_shoot( int texture, const float *pos, int flags, float scale )
 	xh.ref.R_DecalShoot( texture, 0, 0, p, flags, scale );
 }
 
+/* the renderer's R_CreateDecalList slot: n x {position[3], entityIndex, depth, flags, scale, impactPlaneNormal[3], name checksum} */
+int xh_decal_list( float *out, int max )
+{
+	static decallist_t list[MAX_RENDER_DECALS];
+	memset( list, 0, sizeof( list ));
+	int n = xh.ref.R_CreateDecalList( list );
+	if( n > max ) n = max;
+	for( int i = 0; i < n; i++ )
+	{
+		float *f = out + 11 * i;
+		const decallist_t *e = &list[i];
+		unsigned h = 0;
+		for( const char *c = e->name; *c; c++ ) h = h * 31u + (unsigned char)*c;
+		f[0] = e->position[0]; f[1] = e->position[1]; f[2] = e->position[2]; f[3] = e->entityIndex; f[4] = e->depth; f[5] = e->flags;
+		f[6] = e->scale; f[7] = e->impactPlaneNormal[0]; f[8] = e->impactPlaneNormal[1]; f[9] = e->impactPlaneNormal[2]; f[10] = (float)( h & 0xFFFFFu );
+	}
+	return n;
+}
+
 void xh_remove_decals( int texture )
 {
 	xh.ref.R_DecalRemoveAll( texture );

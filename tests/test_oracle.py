@@ -356,6 +356,9 @@ def test_scalar_decals_match_oracle(pkg, scene):
     a, z = emu.render_views(m.cameras[12:40])
     rc, rz = so.render_views(m.cameras[12:40])
     assert np.array_equal(a, rc) and np.array_equal(z, rz), (a == rc).mean()
+    # R_CreateDecalList: what a save game would hold
+    la, lo = emu.decal_list(), so.decal_list()
+    assert len(lo) >= 12 and np.array_equal(la, lo)
     # R_DecalRemoveAll: gone from the lists; blocks built from now on do not carry them
     for r in (emu, so):
         r.remove_decals(0)

@@ -3095,11 +3095,73 @@ static void R_DecalRemoveAll( int texture )
 	}
 }
 
+/* the file's base name: no directories, no extension (COM_FileBase, public/crtlib.c:491) */
+static void rc_file_base( const char *in, char *out, size_t size )
+{
+	out[0] = 0;
+	if( !in || !in[0] || size <= 1 )
+		return;
+	const char *start = in, *dot = NULL, *p;
+	for( p = in; *p; p++ )
+	{
+		if( *p == '/' || *p == '\\' ) start = p + 1;
+		if( *p == '.' ) dot = p;
+	}
+	if( !dot || dot < start )
+		dot = p;
+	const size_t len = Q_min( size - 1, (size_t)( dot - start ));
+	memcpy( out, start, len );
+	out[len] = 0;
+}
+
+static int rc_decal_depth_compare( const void *a, const void *b )
+{
+	const decallist_t *x = a, *y = b;
+	return x->depth > y->depth ? 1 : ( x->depth < y->depth ? -1 : 0 );
+}
+
+/* R_CreateDecalList (r_decals.c:916): the decals of the level for a save game - where, which picture, how deep in its
+ * face's list - without the near-duplicates (same picture and entity within 2 units), lowest depth first */
 static int R_CreateDecalList( struct decallist_s *pList )
 {
-	(void)pList;
-	if( !rc.warned[2] ) { rc.warned[2] = true; gEngfuncs.Con_Reportf( "ref_cuda: R_CreateDecalList (decals in save games) is not built\n" ); }
-	return 0;
+	int total = 0;
+	if( rc.world )
+	{
+		for( int i = 0; i < MAX_RENDER_DECALS; i++ )
+		{
+			const decal_t *d = &rc_decal_pool[i];
+			if( d->psurface == NULL || FBitSet( d->flags, FDECAL_DONTSAVE ))
+				continue;
+			int depth = 0;
+			for( const decal_t *q = d->psurface->pdecals; q && q != d; q = q->pnext )
+				depth++;
+			decallist_t *e = &pList[total];
+			e->depth = depth;
+			e->flags = d->flags;
+			e->scale = d->scale;
+			VectorCopy( d->position, e->position );
+			e->entityIndex = d->entityIndex;
+			if( d->psurface->flags & SURF_PLANEBACK ) VectorNegate( d->psurface->plane->normal, e->impactPlaneNormal );
+			else VectorCopy( d->psurface->plane->normal, e->impactPlaneNormal );
+			rc_file_base( rc.images[( d->texture >= 0 && d->texture < RC_MAX_TEXTURES ) ? d->texture : 0].name, e->name, sizeof( e->name ));
+			/* DecalListAdd: kept unless an entry before it is the same decal again */
+			qboolean merged = false;
+			for( int k = 0; k < total && !merged; k++ )
+				if( !strcmp( e->name, pList[k].name ) && e->entityIndex == pList[k].entityIndex )
+				{
+					vec3_t tmp;
+					VectorSubtract( e->position, pList[k].position, tmp );
+					if( VectorLength( tmp ) < 2 ) /* DECAL_OVERLAP_DISTANCE */
+						merged = true;
+				}
+			if( !merged )
+				total++;
+		}
+		if( gEngfuncs.drawFuncs->R_CreateStudioDecalList )
+			total += gEngfuncs.drawFuncs->R_CreateStudioDecalList( pList, total );
+	}
+	qsort( pList, total, sizeof( decallist_t ), rc_decal_depth_compare );
+	return total;
 }
 
 /* R_ClearAllDecals (r_decals.c:1024): every pool entry leaves its face */

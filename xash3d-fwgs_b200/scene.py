@@ -132,6 +132,14 @@ class Renderer:
         pp = (C.c_float * 3)(*[float(x) for x in pos])
         L.xh_decal_shoot(int(texture), pp, int(flags), float(scale))
 
+    def decal_list(self, max_entries=4096):
+        """the renderer's R_CreateDecalList slot -> rows of {position[3], entity, depth, flags, scale, plane normal[3], name checksum}"""
+        out = np.zeros((max_entries, 11), np.float32)
+        L = self.host.lib
+        L.xh_decal_list.argtypes = [C.c_void_p, C.c_int]
+        n = L.xh_decal_list(out.ctypes.data, max_entries)
+        return out[:n]
+
     def remove_decals(self, texture=0):
         L = self.host.lib
         L.xh_remove_decals.argtypes = [C.c_int]
