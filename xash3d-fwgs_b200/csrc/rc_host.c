@@ -3394,7 +3394,7 @@ static void CL_DrawTracers( double frametime, particle_t *tracers )
 		rc.ntracers++;
 		it->count = 2;
 		it->light = (int32_t)( rc.tri.light << 8 );
-		it->scale = rc_tracer_size[p->type];
+		it->scale = ( (unsigned)p->type < sizeof( rc_tracer_size ) / sizeof( rc_tracer_size[0] )) ? rc_tracer_size[p->type] : 1.0f; /* (the reference indexes past its table for the custom particle types) */
 		VectorCopy( p->org, it->origin );
 		VectorCopy( delta, it->angles );
 		TriTexCoord2f( 0.0f, 0.0f ); it->s0 = rc.tri.s; it->t0 = rc.tri.t;
