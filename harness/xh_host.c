@@ -359,6 +359,13 @@ void xh_decal_shoot( int texture, const float *pos, int flags, float scale )
 	xh.ref.R_DecalShoot( texture, 0, 0, p, flags, scale );
 }
 
+/* the same on a brush entity: world-space point, the entity's number (its model is looked up by the renderer) */
+void xh_decal_shoot_entity( int texture, int entity, const float *pos, int flags, float scale )
+{
+	vec3_t p = { pos[0], pos[1], pos[2] };
+	xh.ref.R_DecalShoot( texture, entity, 0, p, flags, scale );
+}
+
 /* the renderer's R_CreateDecalList slot: n x {position[3], entityIndex, depth, flags, scale, impactPlaneNormal[3], name checksum} */
 int xh_decal_list( float *out, int max )
 {

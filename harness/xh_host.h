@@ -80,6 +80,7 @@ XH_EXPORT int xh_screenshot( int shot_type, void *out, size_t cap, int *width, i
 XH_EXPORT int xh_set_particles( const float *fp, int n );
 /* the renderer's R_DecalShoot slot on the world model (entity 0, model 0): decal texture, centre, FDECAL_* flags, scale */
 XH_EXPORT void xh_decal_shoot( int texture, const float *pos, int flags, float scale );
+XH_EXPORT void xh_decal_shoot_entity( int texture, int entity, const float *pos, int flags, float scale );
 XH_EXPORT int xh_decal_list( float *out, int max );
 XH_EXPORT void xh_remove_decals( int texture );
 XH_EXPORT void xh_clear_decals( void );

@@ -792,3 +792,32 @@ def test_attachments_and_followers_match_oracle(pkg, scene):
             r.add_entity(mi, (0, 0, 0), angles=(0.0, 11.0 * k, 0.0), frame=(5 * k) % 30, movetype=12, aiment=k + 1, animtime=0.4)
         res.append(r.render_views(m.cameras[:16]))
     assert np.array_equal(res[0][0], res[1][0]) and np.array_equal(res[0][1], res[1][1]), ((res[0][0] == res[1][0]).mean(), (res[0][1] == res[1][1]).mean())
+
+
+@pytest.mark.gpu
+def test_decals_on_brush_entities_match_oracle(pkg, scene):
+    """R_DecalShoot on brush entities, on the device: decals hung on faces of rotated and unrotated box submodels ride with them"""
+    m = scene.make_map("small", ncameras=64, brush_models=4)
+    cu = scene.Renderer(pkg.REF_CUDA_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    bare = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    cams = np.asarray(m.cameras[:16], dtype=np.float32).reshape(-1, 6)
+    for r in (cu, so):
+        r.set_time(1.0)
+        scene.add_brush_entities(r, m, cams, 16, rotate=True)
+    nb, _ = bare.render_views(cams)
+    before, bz = so.render_views(cams)
+    spots = []
+    for k in range(len(cams)):
+        ys, xs = np.nonzero(before[k] != nb[k])
+        spots.append((int(np.median(xs)), int(np.median(ys))) if len(xs) else (160, 120))
+    img = scene.sprite_image(5, 32, 32)
+    for r in (cu, so):
+        tex = r.load_pic("{entdecal", img, 1 << 16)
+        for k, c in enumerate(cams):
+            r.decal_shoot_entity(tex, k + 1, scene.pixel_point(c, bz[k], spots[k][0], spots[k][1]), 0, 1.0)
+    so.gamma_changed()  # see test_decals_match_oracle
+    rc, rz = so.render_views(cams)
+    cc, cz = cu.render_views(cams)
+    assert (rc != before).mean() > 0.001
+    assert np.array_equal(cc, rc) and np.array_equal(cz, rz), ((cc == rc).mean(), (cz == rz).mean())

@@ -419,3 +419,37 @@ def test_scalar_follower_models_match_oracle(pkg, scene):
     nb, _ = bare.render_views(m.cameras[:6])
     assert (res[1][0] != nb).mean() > 0.002, "the oracle drew no follower"
     assert np.array_equal(res[0][0], res[1][0]) and np.array_equal(res[0][1], res[1][1]), (res[0][0] == res[1][0]).mean()
+
+
+def test_scalar_decals_on_brush_entities_match_oracle(pkg, scene):
+    """R_DecalShoot on brush entities (r_decals.c:736-779): the point goes into the entity's own space (rotated ones through the
+    inverse of its matrix), the decal hangs on a face of the submodel and rides with it"""
+    m = scene.make_map("small", ncameras=64, brush_models=4)
+    emu = scene.Renderer(EMU_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    cams = np.asarray(m.cameras[:10], dtype=np.float32).reshape(-1, 6)
+    for r in (emu, so):
+        r.set_time(1.0)
+        scene.add_brush_entities(r, m, cams, 10, rotate=True)
+    bare = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    nb, _ = bare.render_views(cams)
+    before, bz = so.render_views(cams)
+    # a pixel of every view that shows its entity: the middle of the pixels the entities changed
+    spots = []
+    for k in range(len(cams)):
+        ys, xs = np.nonzero(before[k] != nb[k])
+        spots.append((int(np.median(xs)), int(np.median(ys))) if len(xs) else (160, 120))
+    rng = np.random.default_rng(3)
+    img = np.zeros((32, 32, 4), np.uint8)
+    img[..., 0] = 255; img[..., 1] = rng.integers(0, 255, (32, 32)); img[..., 3] = rng.integers(0, 255, (32, 32)); img[8:24, 8:24, 3] = 255
+    for r in (emu, so):
+        tex = r.load_pic("{entdecal", img, 1 << 16)
+        for k, c in enumerate(cams):
+            pt = scene.pixel_point(c, bz[k], spots[k][0], spots[k][1])
+            r.decal_shoot_entity(tex, k + 1, pt, 0, 1.0)
+    so.gamma_changed()
+    rc, rz = so.render_views(cams)
+    a, z = emu.render_views(cams)
+    assert (rc != before).mean() > 0.001, "no decal landed on a brush entity"
+    assert np.array_equal(a, rc) and np.array_equal(z, rz), (a == rc).mean()
+    assert np.array_equal(emu.decal_list(), so.decal_list())

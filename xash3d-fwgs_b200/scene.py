@@ -124,6 +124,14 @@ class Renderer:
         got = L.xh_get_tracers(out.ctypes.data)
         return out[:got]
 
+    def decal_shoot_entity(self, texture, entity, pos, flags=0, scale=1.0):
+        """R_DecalShoot on a brush entity (its number as add_entity returned it), pos in world space"""
+        L = self.host.lib
+        L.xh_decal_shoot_entity.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_float]
+        L.xh_decal_shoot_entity.restype = None
+        pp = (C.c_float * 3)(*[float(x) for x in pos])
+        L.xh_decal_shoot_entity(int(texture), int(entity), pp, int(flags), float(scale))
+
     def decal_shoot(self, texture, pos, flags=0, scale=1.0):
         """the renderer's R_DecalShoot slot on the world model: a decal texture (load_pic) stamped at pos"""
         L = self.host.lib
@@ -532,6 +540,19 @@ def compare_frames(a_col, a_z, b_col, b_z):
     same_c = float((a_col == b_col).mean())
     same_z = float((a_z == b_z).mean()) if a_z is not None and b_z is not None else 1.0
     return same_c, same_z
+
+
+def pixel_point(cam, z, x, y, fov_x=90.0):
+    """the world point a pixel of a frame shows: cam = {origin, pitch, yaw, roll = 0}, z = that frame's 1/z buffer"""
+    h, w = z.shape
+    depth = 32768.0 / max(int(z[y, x]), 1)  # the z buffer holds 0x8000 / depth along the view axis
+    p, yw = np.radians(cam[3]), np.radians(cam[4])
+    fwd = np.array([np.cos(p) * np.cos(yw), np.cos(p) * np.sin(yw), -np.sin(p)])
+    right = np.array([np.sin(yw), -np.cos(yw), 0.0])
+    up = np.array([np.sin(p) * np.cos(yw), np.sin(p) * np.sin(yw), np.cos(p)])
+    scale = (w / 2.0) / math.tan(math.radians(fov_x) / 2.0)
+    d = fwd + right * ((x - (w / 2.0 - 0.5)) / scale) - up * ((y - (h / 2.0 - 0.5)) / scale)
+    return np.asarray(cam[:3], dtype=np.float64) + d * depth
 
 
 def shoot_decals(r, cams, z, seed=5, scale=1.0, opaque=False):

@@ -658,6 +658,18 @@ def generate(spec: MapSpec = MapSpec(), ncameras: int = 256) -> GeneratedMap:
         maxs = [b.world(a, box[a * 2 + 1]) for a in range(3)]
         ch = [c if c >= 0 else c for c in n["children"]]  # negative = -(leaf+1) already
         node_blob += struct.pack("<i2h3h3hHH", n["plane"], ch[0], ch[1], *mins, *maxs, n["firstface"], n["numfaces"])
+    # brush submodels: a chain of six nodes each, one per face plane - outside of a plane ends in a leaf, inside goes on to the
+    # next plane (the engine walks a submodel's own tree from headnode[0]: decal placement, R_DecalNode)
+    sub_heads = []
+    nnodes_total = len(b.nodes)
+    for (mn, mx, ff, nf) in submodels:
+        sub_heads.append(nnodes_total)
+        for q in range(nf):
+            planenum, side = face_recs[ff + q][0], face_recs[ff + q][1]
+            nxt = nnodes_total + 1 if q + 1 < nf else -1  # -1 = -(leaf 0 + 1)
+            ch = (-1, nxt) if side == 0 else (nxt, -1)
+            node_blob += struct.pack("<i2h3h3hHH", planenum, ch[0], ch[1], *[int(v) for v in mn], *[int(v) for v in mx], ff + q, 1)
+            nnodes_total += 1
     L[5] = bytes(node_blob)
     L[6] = b"".join(struct.pack("<8fihh", *ti[:8], ti[8], ti[9], -1) for ti in texinfo)
     L[7] = b"".join(struct.pack("<HhihH4Bi", p, s, fe, ne, ti, *st, lo) for (p, s, fe, ne, ti, st, lo) in face_recs)
@@ -672,9 +684,9 @@ def generate(spec: MapSpec = MapSpec(), ncameras: int = 256) -> GeneratedMap:
     wmins = [b.world(a, 0) for a in range(3)]
     wmaxs = [b.world(a, g.shape[a]) for a in range(3)]
     L[14] = struct.pack("<9f4i3i", *map(float, wmins), *map(float, wmaxs), 0.0, 0.0, 0.0, 0, 0, 0, 0, nvis, 0, nworldfaces)
-    for (mn, mx, ff, nf) in submodels:
-        L[14] += struct.pack("<9f4i3i", *mn, *mx, 0.0, 0.0, 0.0, 0, 0, 0, 0, 0, ff, nf)
-    assert len(verts) < 65536 and len(face_recs) < 65536 and len(marks) < 65536 and len(b.nodes) < 32768 and nleafs < 32768
+    for k, (mn, mx, ff, nf) in enumerate(submodels):
+        L[14] += struct.pack("<9f4i3i", *mn, *mx, 0.0, 0.0, 0.0, sub_heads[k], 0, 0, 0, 0, ff, nf)
+    assert len(verts) < 65536 and len(face_recs) < 65536 and len(marks) < 65536 and nnodes_total < 32768 and nleafs < 32768
     out = bytearray(struct.pack("<i", 30) + b"\0" * (8 * 15))
     for i in range(15):
         while len(out) % 4:
