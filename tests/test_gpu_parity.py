@@ -821,3 +821,33 @@ def test_decals_on_brush_entities_match_oracle(pkg, scene):
     cc, cz = cu.render_views(cams)
     assert (rc != before).mean() > 0.001
     assert np.array_equal(cc, rc) and np.array_equal(cz, rz), ((cc == rc).mean(), (cz == rz).mean())
+
+
+@pytest.mark.gpu
+def test_sliced_graph_batches_with_effects_match_oracle(pkg, scene):
+    """a batch large enough for the sliced path (>= 64 views with host output: slices on two streams, segments replayed from
+    CUDA graphs) carrying decals, glow sprites, tracers, particles and brush entities; rendered twice (capture, then replay),
+    then again after more decals (the graphs' arguments change)"""
+    m = scene.make_map("small", ncameras=64, brush_models=4)
+    cu = scene.Renderer(pkg.REF_CUDA_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    cams = np.concatenate([np.asarray(m.cameras[:64], dtype=np.float32).reshape(-1, 6)] * 2)[:96]
+    _, bz = so.render_views(cams[:16])
+    for r in (cu, so):
+        r.set_time(1.0)
+        scene.add_brush_entities(r, m, cams[20:], 6, rotate=True)
+        scene.add_glow_sprites(r, cams, 32)
+        scene.add_tracers(r, cams, 64)
+        scene.add_particles(r, cams, 128, ahead=40.0)
+        scene.shoot_decals(r, cams[:8], bz[:8])
+    so.gamma_changed()
+    rc, rz = so.render_views(cams)
+    for _ in range(2):
+        cc, cz = cu.render_views(cams)
+        assert np.array_equal(cc, rc) and np.array_equal(cz, rz), ((cc == rc).mean(), (cz == rz).mean())
+    for r in (cu, so):
+        scene.shoot_decals(r, cams[8:16], bz[8:16], seed=9)
+    so.gamma_changed()
+    rc, rz = so.render_views(cams)
+    cc, cz = cu.render_views(cams)
+    assert np.array_equal(cc, rc) and np.array_equal(cz, rz), ((cc == rc).mean(), (cz == rz).mean())
