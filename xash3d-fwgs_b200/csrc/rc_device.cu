@@ -876,6 +876,7 @@ struct Dev
 	struct batch_graph_t { cudaGraphExec_t exec = nullptr; unsigned long long key = 0, launches = 0; };
 	batch_graph_t graphs[4][2]; /* [segment][frame buffer set] */
 	bool use_graphs = true;
+	int ev_threads = 0; /* RC_EV_THREADS: k_events block size forced (measurement only) */
 	int tr_strips = TR_STRIPS; /* horizontal strips of a frame in k_tris_ordered (RC_TR_STRIPS: measurement only) */
 	cudaEvent_t ev_join[2] = {};
 	std::vector<rc_view_t> pend_views; int pend_w = 0, pend_h = 0, pend_clear = 0; uint16_t *pend_color = nullptr; int16_t *pend_z = nullptr;
@@ -1268,7 +1269,12 @@ int launch_slice( const rc_work_t &ws, int k, cudaStream_t st, cudaEvent_t *evs,
 	const int nlines = ws.nviews * ws.height;
 	{
 		dim3 g( ws.nviews, ws.nbands ); /* x = view: blocks are issued band by band, see k_events */
-		k_events<<<g, EV_THREADS, rc_events_smem( ws.ev_ecap, ws.scanbits_words ), st>>>( ws ); D.launches++;
+		/* wide frames of large maps: more threads per band block (few blocks, thousands of edges each) */
+		const int evt = D.ev_threads ? D.ev_threads : ( ws.width > 640 ? 1024 : 256 );
+		if( evt == 1024 ) k_events<1024><<<g, 1024, rc_events_smem( ws.ev_ecap, ws.scanbits_words ), st>>>( ws );
+		else if( evt == 512 ) k_events<512><<<g, 512, rc_events_smem( ws.ev_ecap, ws.scanbits_words ), st>>>( ws );
+		else k_events<256><<<g, 256, rc_events_smem( ws.ev_ecap, ws.scanbits_words ), st>>>( ws );
+		D.launches++;
 		KCHECK( "k_events", st );
 		const int lblocks = ( nlines + LN_WARPS - 1 ) / LN_WARPS;
 		k_lines<<<lblocks < LN_GRID ? lblocks : LN_GRID, LN_WARPS * 32, 0, st>>>( ws ); D.launches++;
@@ -1475,13 +1481,16 @@ int rc_dev_init( int device )
 	CK( cudaEventCreateWithFlags( &D.ev_fork, cudaEventDisableTiming ));
 	for( auto &e : D.ev_join ) CK( cudaEventCreateWithFlags( &e, cudaEventDisableTiming ));
 	D.use_graphs = getenv( "RC_NO_GRAPHS" ) == nullptr;
+	if( const char *e = getenv( "RC_EV_THREADS" )) { const int n = atoi( e ); if( n == 256 || n == 512 || n == 1024 ) D.ev_threads = n; }
 	if( const char *e = getenv( "RC_TR_STRIPS" )) { const int n = atoi( e ); if( n >= 1 && n <= 64 ) D.tr_strips = n; }
 	for( auto &ss : D.slice_stream ) CK( cudaStreamCreateWithFlags( &ss, cudaStreamNonBlocking ));
 	for( auto &ss : D.aux_stream ) CK( cudaStreamCreateWithFlags( &ss, cudaStreamNonBlocking ));
 	for( auto &e : D.ev_cache ) { CK( cudaEventCreate( &e[0] )); CK( cudaEventCreate( &e[1] )); }
 	for( auto &e : D.ev ) CK( cudaEventCreate( &e ));
 	CK( cudaFuncSetAttribute( k_viswalk<VW_NTHREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 64 ));
-	CK( cudaFuncSetAttribute( k_events, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_events_smem( EV_ECAP_BIG, 65536 / 32 + 2 )));
+	CK( cudaFuncSetAttribute( k_events<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_events_smem( EV_ECAP_BIG, 65536 / 32 + 2 )));
+	CK( cudaFuncSetAttribute( k_events<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_events_smem( EV_ECAP_BIG, 65536 / 32 + 2 )));
+	CK( cudaFuncSetAttribute( k_events<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_events_smem( EV_ECAP_BIG, 65536 / 32 + 2 )));
 	CK( cudaFuncSetAttribute( k_draw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_draw_smem( 8192, 1 )));
 	for( int i = 0; i < 256; i++ ) D.h_styles[i] = 256;
 	if( upload( &D.d_styles, D.h_styles, 256 ) != 0 ) return -1;

@@ -22,8 +22,8 @@
 #define RC_K_SPANS_CUH
 
 /* SP_LINES (scanlines per band) is defined by rc_device.cu */
-#define EV_THREADS  256
-#define EV_WARPS    ( EV_THREADS / 32 )
+/* k_events is built for 256 threads (frames up to 640 wide: a few hundred edges per band) and for 512 / 1024 (wide frames of
+ * large maps: thousands of edges per band, few blocks - C3: spans 1.38 -> 1.01 ms with 512; 256 stays faster on C2 / C5) */
 #define LN_WARPS    4
 #define LN_HEAVY    128  /* events: lines above are listed by k_events and go first (measured: 32: 166 us, 64: 159, 128: 153, 192: 159) */
 #define LN_CHUNK    1    /* scanlines a warp takes from the shared cursor at a time (measured on the C2 batch: 1: 170 us, 2: 172, 4: 183, 8: 184) */
@@ -51,11 +51,12 @@ static inline size_t rc_events_smem( int32_t ecap, int32_t bitwords )
 	return sizeof( rc_edge_t ) * (size_t)ecap + sizeof( unsigned long long ) * (size_t)ecap + sizeof( uint32_t ) * 2 * ( (size_t)bitwords + 1 );
 }
 
-__global__ void __launch_bounds__( EV_THREADS, 4 ) k_events( rc_work_t w )
+template <int EV_THREADS>
+__global__ void __launch_bounds__( EV_THREADS, 1024 / EV_THREADS ) k_events( rc_work_t w )
 {
 	extern __shared__ __align__( 16 ) unsigned char ev_smem[];
-	__shared__ int32_t s_wcnt[EV_WARPS][SP_LINES];
-	__shared__ int32_t s_warp[EV_WARPS];
+	__shared__ int32_t s_wcnt[( EV_THREADS / 32 )][SP_LINES];
+	__shared__ int32_t s_warp[( EV_THREADS / 32 )];
 	__shared__ int32_t s_ne;
 	rc_edge_t *s_edge = reinterpret_cast<rc_edge_t *>( ev_smem );
 	unsigned long long *s_key = reinterpret_cast<unsigned long long *>( ev_smem + sizeof( rc_edge_t ) * (size_t)w.ev_ecap );
@@ -177,7 +178,7 @@ __global__ void __launch_bounds__( EV_THREADS, 4 ) k_events( rc_work_t w )
 		if( lane == 31 ) s_warp[warp] = x;
 		__syncthreads();
 		int32_t wbase = 0, tot = 0;
-		for( int k = 0; k < EV_WARPS; k++ )
+		for( int k = 0; k < ( EV_THREADS / 32 ); k++ )
 		{
 			if( k < warp ) wbase += s_warp[k];
 			tot += s_warp[k];
@@ -235,7 +236,7 @@ __global__ void __launch_bounds__( EV_THREADS, 4 ) k_events( rc_work_t w )
 
 	EV_MARK(); /* 4: local numbers */
 	/* 1. events per line: every warp takes a contiguous run of the sorted edge list */
-	const int32_t per = ( ne + EV_WARPS - 1 ) / EV_WARPS;
+	const int32_t per = ( ne + ( EV_THREADS / 32 ) - 1 ) / ( EV_THREADS / 32 );
 	const int32_t k0 = warp * per, k1 = min( ne, k0 + per );
 	int32_t cnt = 0;
 	for( int32_t k = k0; k < k1; k++ )
@@ -246,7 +247,7 @@ __global__ void __launch_bounds__( EV_THREADS, 4 ) k_events( rc_work_t w )
 	s_wcnt[warp][lane] = cnt;
 	__syncthreads();
 	int32_t mybase = 0, n = 0;
-	for( int k = 0; k < EV_WARPS; k++ )
+	for( int k = 0; k < ( EV_THREADS / 32 ); k++ )
 	{
 		const int32_t c = s_wcnt[k][lane];
 		if( k < warp ) mybase += c;
