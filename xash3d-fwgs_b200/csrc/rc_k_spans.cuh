@@ -30,7 +30,7 @@
 #define SP_SORTCAP  512  /* events per line k_lines sorts in shared memory; longer lines go to k_lines_wide */
 #define WD_SORTCAP  4096 /* events per line k_lines_wide sorts in shared memory (a block per line); beyond: serial */
 #define WD_THREADS  128
-#define WD_GRID     ( 148 * 4 )
+#define WD_GRID     ( 148 * 6 )
 #define RC_LINE_WIDE 0x20000000 /* set in nsp by k_events: more events than k_lines sorts or more band-local surfaces than its
                                  * register bit sets hold - the line is k_lines_wide's */
 #define SP_BITWORDS 64   /* shared-memory bit-set words per line (views listing <= 2015 faces), else global scratch */
