@@ -876,6 +876,7 @@ struct Dev
 	struct batch_graph_t { cudaGraphExec_t exec = nullptr; unsigned long long key = 0, launches = 0; };
 	batch_graph_t graphs[4][2]; /* [segment][frame buffer set] */
 	bool use_graphs = true;
+	bool vw_wide = false; /* k_viswalk<1024> for few views of a large tree */
 	int ev_threads = 0; /* RC_EV_THREADS: k_events block size forced (measurement only) */
 	int tr_strips = TR_STRIPS; /* horizontal strips of a frame in k_tris_ordered (RC_TR_STRIPS: measurement only) */
 	cudaEvent_t ev_join[2] = {};
@@ -1058,6 +1059,7 @@ int ensure_batch( int nviews, int width, int height )
 			}
 		}
 		D.vw_grid = per_sm * D.num_sms;
+		D.vw_wide = getenv( "RC_VW_WIDE" ) ? atoi( getenv( "RC_VW_WIDE" )) != 0 : ( sc.numnodes >= 4096 );
 	}
 
 	int k = 0;
@@ -1226,6 +1228,10 @@ int launch_slice( const rc_work_t &ws, int k, cudaStream_t st, cudaEvent_t *evs,
 	if( D.nbents ) fill32( ws.viewbm, 0u, (size_t)ws.nviews, st );
 	if( D.nbents ) fill32( ws.leafbase, 0xFFFFFFFFu, (size_t)ws.nviews * sc.numleafs, st );
 	if( evs ) CK( cudaEventRecord( evs[0], st ));
+	/* a handful of views of a large map (C3: 8 views, 15 k nodes, levels thousands of nodes wide): 1024 threads per view */
+	if( D.vw_wide && ws.nviews <= D.num_sms )
+		k_viswalk<1024><<<ws.nviews < D.vw_grid ? ws.nviews : D.vw_grid, 1024, (size_t)ws.vis_smem, st>>>( sc, ws );
+	else
 	k_viswalk<VW_NTHREADS><<<ws.nviews < D.vw_grid ? ws.nviews : D.vw_grid, VW_NTHREADS, (size_t)ws.vis_smem, st>>>( sc, ws );
 	D.launches++;
 	KCHECK( "k_viswalk", st );
@@ -1488,6 +1494,7 @@ int rc_dev_init( int device )
 	for( auto &e : D.ev_cache ) { CK( cudaEventCreate( &e[0] )); CK( cudaEventCreate( &e[1] )); }
 	for( auto &e : D.ev ) CK( cudaEventCreate( &e ));
 	CK( cudaFuncSetAttribute( k_viswalk<VW_NTHREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 64 ));
+	CK( cudaFuncSetAttribute( k_viswalk<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 64 ));
 	CK( cudaFuncSetAttribute( k_events<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_events_smem( EV_ECAP_BIG, 65536 / 32 + 2 )));
 	CK( cudaFuncSetAttribute( k_events<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_events_smem( EV_ECAP_BIG, 65536 / 32 + 2 )));
 	CK( cudaFuncSetAttribute( k_events<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_events_smem( EV_ECAP_BIG, 65536 / 32 + 2 )));
