@@ -1810,7 +1810,7 @@ int rc_dev_set_studio( const rc_spart_t *parts, int nparts, const float *bones, 
 	if( upload_keep( &D.d_parts, parts, (size_t)nparts ) != 0 ) return -1;
 	if( upload_keep( &D.d_bones, bones, (size_t)nbones * 12 ) != 0 ) return -1;
 	if( upload_keep( &D.d_blight, blightvecs, (size_t)nbones * 3 ) != 0 ) return -1;
-	if( (size_t)totalverts * 3 > D.cap_mvpos ) { if( dalloc( &D.d_mvpos, (size_t)totalverts * 3 ) != 0 ) return -1; D.cap_mvpos = (size_t)totalverts * 3; }
+	if( (size_t)totalverts * 4 > D.cap_mvpos ) { if( dalloc( &D.d_mvpos, (size_t)totalverts * 4 ) != 0 ) return -1; D.cap_mvpos = (size_t)totalverts * 4; } /* float4 per vertex */
 	if( (size_t)totalnorms > D.cap_mlight ) { if( dalloc( &D.d_mlight, (size_t)totalnorms ) != 0 ) return -1; D.cap_mlight = (size_t)totalnorms; }
 	D.h2d_bytes += sizeof( rc_spart_t ) * (size_t)nparts + sizeof( float ) * 15 * (size_t)nbones;
 	if( (size_t)nparts * 6 > D.cap_partbox ) { if( dalloc( &D.d_partbox, (size_t)nparts * 6 + 6 ) != 0 ) return -1; D.cap_partbox = (size_t)nparts * 6; }

@@ -106,9 +106,12 @@ __device__ __forceinline__ int rc_item_corners( const rc_work_t &w, const rc_vie
 #pragma unroll
 		for( int q = 0; q < 3; q++ )
 		{
-			const rc_mcorner_t m = mc[q];
-			const float *p = w.mvpos + (size_t)( it->vert_base + m.vert ) * 3;
-			c[q].xyz[0] = p[0]; c[q].xyz[1] = p[1]; c[q].xyz[2] = p[2];
+			/* one 8-byte load for the corner record, one 16-byte load for the vertex (k_studio_points leaves float4s) */
+			union { uint2 raw; rc_mcorner_t m; } u;
+			u.raw = __ldg( reinterpret_cast<const uint2 *>( mc + q ));
+			const rc_mcorner_t m = u.m;
+			const float4 p = __ldg( reinterpret_cast<const float4 *>( w.mvpos ) + ( it->vert_base + m.vert ));
+			c[q].xyz[0] = p.x; c[q].xyz[1] = p.y; c[q].xyz[2] = p.z;
 			c[q].l = w.mlight[it->light_base + m.norm]; c[q].s = m.s; c[q].t = m.t;
 			if( it->chrome )
 			{
@@ -168,8 +171,7 @@ __global__ void __launch_bounds__( 256 ) k_studio_points( rc_scene_t sc, rc_work
 		if( i >= pt.numverts ) return;
 		float out[3];
 		rc_studio_vertex( w.bones + (size_t)( pt.bones + w.sstatic[pt.svertbone + i] ) * 12, sf + pt.sverts + 3 * i, out );
-		float *dst = w.mvpos + (size_t)idx * 3;
-		dst[0] = out[0]; dst[1] = out[1]; dst[2] = out[2];
+		reinterpret_cast<float4 *>( w.mvpos )[idx] = make_float4( out[0], out[1], out[2], 0.0f );
 		/* the part's bounding box for k_item_cull: order-preserving int keys, one atomic pair per axis (per warp when the
 		 * whole warp works on one part) */
 		const unsigned am = __activemask();
