@@ -851,3 +851,21 @@ def test_sliced_graph_batches_with_effects_match_oracle(pkg, scene):
     rc, rz = so.render_views(cams)
     cc, cz = cu.render_views(cams)
     assert np.array_equal(cc, rc) and np.array_equal(cz, rz), ((cc == rc).mean(), (cz == rz).mean())
+
+
+@pytest.mark.gpu
+def test_coincident_edges_match_oracle(pkg, scene):
+    """VERDICT round 1, weak 4 (equal-u ties) on the device: boxes standing exactly on the floor, touching side by side and
+    stacked (coincident edges of different surfaces, 1/z ties between pieces), 32 cameras + the same from 60 units closer"""
+    m = scene.make_map("small", ncameras=64, brush_models=4)
+    cu = scene.Renderer(pkg.REF_CUDA_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    cams = np.asarray(m.cameras[:32], dtype=np.float32).reshape(-1, 6).copy()
+    for r in (cu, so):
+        r.set_time(1.0)
+        scene.add_abutting_boxes(r, m, cams)
+    fwd = np.stack([np.cos(np.radians(cams[:, 4])), np.sin(np.radians(cams[:, 4])), np.zeros(len(cams))], -1)
+    views = np.concatenate([cams, np.concatenate([cams[:, :3] + 60.0 * fwd, cams[:, 3:]], -1)]).astype(np.float32)
+    cc, cz = cu.render_views(views)
+    rc, rz = so.render_views(views)
+    assert np.array_equal(cc, rc) and np.array_equal(cz, rz), ((cc == rc).mean(), (cz == rz).mean())

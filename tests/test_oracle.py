@@ -453,3 +453,24 @@ def test_scalar_decals_on_brush_entities_match_oracle(pkg, scene):
     assert (rc != before).mean() > 0.001, "no decal landed on a brush entity"
     assert np.array_equal(a, rc) and np.array_equal(z, rz), (a == rc).mean()
     assert np.array_equal(emu.decal_list(), so.decal_list())
+
+
+def test_scalar_coincident_edges_match_oracle(pkg, scene):
+    """equal-u ties. Boxes whose faces lie in the floor's plane, touch each other and share edge lines
+    (coincident edges of different surfaces, 1/z ties between pieces) seen from 24 cameras, some very close (edges clamped to
+    the screen border): every pixel as ref_soft orders them"""
+    m = scene.make_map("small", ncameras=64, brush_models=4)
+    emu = scene.Renderer(EMU_PATH, 320, 240, m)
+    so = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    cams = np.asarray(m.cameras[:24], dtype=np.float32).reshape(-1, 6).copy()
+    for r in (emu, so):
+        r.set_time(1.0)
+        scene.add_abutting_boxes(r, m, cams[:12])
+    near = cams.copy()  # views 12..23: the first twelve again from 60 units closer
+    near[12:] = np.concatenate([cams[:12, :3] + 60.0 * np.stack([np.cos(np.radians(cams[:12, 4])), np.sin(np.radians(cams[:12, 4])), np.zeros(12)], -1), cams[:12, 3:]], -1)
+    a, az = emu.render_views(near)
+    rc, rz = so.render_views(near)
+    bare = scene.Renderer(pkg.REF_SOFT_PATH, 320, 240, m)
+    nb, _ = bare.render_views(near)
+    assert (rc != nb).mean() > 0.05, "the boxes are not in view"
+    assert np.array_equal(a, rc) and np.array_equal(az, rz), ((a == rc).mean(), (az == rz).mean())

@@ -430,6 +430,22 @@ def add_brush_entities(r, m, cams, count=16, ahead=88.0, drop=24.0, rotate=True,
         r.add_entity(models[k % len(models)]["modelindex"], org, angles=ang, rendermode=rendermode, renderamt=renderamt)
 
 
+def add_abutting_boxes(r, m, cams):
+    """brush entities placed to make coincident edges: every box stands exactly on the floor (its bottom face in the floor's
+    plane), and a second box of the same submodel touches it side by side (shared face plane, collinear top and bottom edges)"""
+    models = m.extras["brush_models"]
+    cams = np.asarray(cams, dtype=np.float32).reshape(-1, 6)
+    for k, c in enumerate(cams):
+        md = models[k % len(models)]
+        yaw = np.radians(float(c[4]))
+        floor = float(c[2]) - 56.0
+        org = np.array([round(c[0] + 96.0 * np.cos(yaw)), round(c[1] + 96.0 * np.sin(yaw)), floor - md["mins"][2]])
+        r.add_entity(md["modelindex"], tuple(org))
+        r.add_entity(md["modelindex"], (org[0] + (md["maxs"][0] - md["mins"][0]), org[1], org[2]))
+        if k % 3 == 0:  # a third one on top: coincident horizontal faces
+            r.add_entity(md["modelindex"], (org[0], org[1], org[2] + (md["maxs"][2] - md["mins"][2])))
+
+
 def add_mixed_brush_entities(r, m, cams):
     """opaque, blended (kRenderTransTexture), additive and alpha-tested brush entities in front of the first 26 cameras"""
     add_brush_entities(r, m, cams, 8, rotate=True)
